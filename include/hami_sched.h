@@ -1,0 +1,281 @@
+/*
+ * hami_sched.h — C ABI of the B200-native HAMi Filter/Score engine.
+ *
+ * This is the drop-in boundary for ONE path of the reference scheduler
+ * (soitun/k8s-vgpu-scheduler == Project-HAMi/HAMi v2.10.0): the block
+ *   getNodesUsage + calcScore + sort.Sort/take-last + commit
+ * inside Scheduler.Filter (pkg/scheduler/scheduler.go:1067-1154).  A Go
+ * maintainer binds these entry points with cgo; every
+ * argument is a caller-owned plain buffer that is copied before the call
+ * returns, nothing calls back into the host language and no host pointer is
+ * retained (cgo pointer rules).
+ *
+ * All paths in comments are relative to the reference tree root.
+ *
+ * Threading: a handle is thread-compatible, not thread-safe.  The reference
+ * runs one scheduling cycle at a time; the cgo shim serialises calls with one
+ * mutex, which also gives the deterministic order parity needs.
+ *
+ * Result memory returned through hs_filter_result / hs_batch_get is owned by
+ * the handle and stays valid until the next call on that handle.
+ */
+#ifndef HAMI_SCHED_H_
+#define HAMI_SCHED_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HS_MAX_DEVICES_PER_NODE 8   /* device slots per node held in HBM (reference asserts <=12 for stable sort, F6) */
+#define HS_MAX_TYPES 64             /* distinct device model strings interned per handle */
+#define HS_MAX_REQS_PER_POD 16      /* (container, vendor) request entries evaluated on the device per pod */
+#define HS_MAX_CONTAINERS 16        /* init + app containers per pod */
+
+/* ---- status codes ------------------------------------------------------ */
+enum {
+  HS_OK = 0,
+  HS_FIT = 0,            /* a node was chosen and committed               */
+  HS_NOFIT = 1,          /* no node fits: FailedNodes is filled, no commit (scheduler.go:1109-1114) */
+  HS_PASSTHROUGH = 2,    /* pod requests no HAMi resource: every candidate passes (scheduler.go:1080-1087) */
+  HS_ERR_INVALID = -1,   /* malformed argument / unsupported shape        */
+  HS_ERR_CUDA = -2,      /* CUDA runtime failure; see hs_last_error       */
+  HS_ERR_UNSUPPORTED = -3,/* feature outside the built scope (MIG, quota…) */
+  HS_ERR_WEIGHTS = -4,   /* invalid hami.io/device-scoring-weights: whole Filter errors (score.go:361-364) */
+  HS_ERR_NOTFOUND = -5
+};
+
+/* Fixed reason vocabulary of pkg/device/common/common.go:25-44, in this order. */
+enum {
+  HS_R_CardTypeMismatch = 0,
+  HS_R_CardUuidMismatch,
+  HS_R_CardTimeSlicingExhausted,
+  HS_R_CardComputeUnitsExhausted,
+  HS_R_CardInsufficientMemory,
+  HS_R_CardInsufficientCore,
+  HS_R_CardNotHealth,
+  HS_R_CardCordoned,
+  HS_R_NumaNotFit,
+  HS_R_ExclusiveDeviceAllocateConflict,
+  HS_R_CardNotFoundCustomFilterRule,
+  HS_R_CardMigTopologyInfeasible,
+  HS_R_AllocatedCardsInsufficientRequest,
+  HS_R_ResourceQuotaNotFit,
+  HS_R_ModeNotFit,
+  HS_R_COUNT
+};
+
+/* ---- inventory --------------------------------------------------------- */
+
+/* device.DeviceInfo (pkg/device/devices.go:127-144) as the register path hands
+ * it to nodeManager.addNode (pkg/scheduler/nodes.go:76).                    */
+typedef struct hs_device_info {
+  const char* id;        /* UUID                                          */
+  uint32_t    index;     /* DeviceInfo.Index                              */
+  int32_t     count;     /* split count (slots)                           */
+  int32_t     devmem;    /* MiB                                           */
+  int32_t     devcore;   /* percent (or aiCore for Ascend)                */
+  const char* type;      /* model string, e.g. "NVIDIA A100-SXM4-80GB"    */
+  int32_t     numa;
+  const char* mode;      /* "hami-core" | "mig" | "mps" | ""              */
+  uint8_t     health;
+  const char* vendor;    /* DevicesMap key == CommonWord(): "NVIDIA", "DCU", "MLU", "Ascend910B3", … */
+  int32_t     network_id;/* CustomInfo["NetworkID"] (Ascend), -1 = absent */
+} hs_device_info;
+
+/* device.NodeInfo (pkg/device/devices.go:170-174) plus the node annotations the
+ * hot path reads.  Devices are listed vendor by vendor in sorted vendor-key
+ * order, registration order inside a vendor (canonical rule 5). */
+typedef struct hs_node_info {
+  const char*           name;
+  const hs_device_info* devices;
+  uint32_t              n_devices;
+  /* NVIDIA pair scores from annotation hami.io/node-nvidia-score
+   * (nvidia/device.go:43,319-340): row-major n_devices x n_devices,
+   * pair_scores[i*n+j] = DevicePairScore{ID=i}.Scores[j]; NULL = none (0). */
+  const int32_t*        pair_scores;
+  const char*           device_cordon;  /* annotation hami.io/device-cordon (nvidia/device.go:59), NULL = absent */
+  int8_t                hami_vnpu_core; /* annotation hami-vnpu-core: -1 absent, 1 == "true", 0 any other value (ascend/device.go:463-467) */
+} hs_node_info;
+
+/* ---- pod --------------------------------------------------------------- */
+
+/* device.ContainerDeviceRequest (pkg/device/devices.go:222-228), i.e. the
+ * output of <vendor>.GenerateResourceRequests; `key` is the map key it is
+ * stored under in ContainerDeviceRequests (devices.go:659,677).             */
+typedef struct hs_container_request {
+  const char* key;
+  const char* type;
+  int32_t     nums;
+  int32_t     memreq;
+  int32_t     mempct;    /* MemPercentagereq; 101 = unset (nvidia/device.go:551) */
+  int32_t     coresreq;
+} hs_container_request;
+
+typedef struct hs_container {
+  const hs_container_request* reqs;
+  uint32_t                    n_reqs;
+} hs_container;
+
+typedef struct hs_kv {
+  const char* key;
+  const char* value;
+} hs_kv;
+
+/* The parts of *corev1.Pod that Filter reads: UID, namespace, annotations,
+ * and Resourcereqs(pod) (devices.go:639-691): init containers first.       */
+typedef struct hs_pod {
+  const char*         uid;
+  const char*         ns;
+  const char*         name;
+  const hs_kv*        annotations;
+  uint32_t            n_annotations;
+  const hs_container* containers;
+  uint32_t            n_containers;
+  uint32_t            n_init;     /* len(pod.Spec.InitContainers) */
+} hs_pod;
+
+/* ---- results ----------------------------------------------------------- */
+
+/* device.ContainerDevice (pkg/device/devices.go:205-216), flattened with the
+ * container index and the PodDevices map key it belongs to.  Entries are raw
+ * (un-collapsed), ordered by type key, then container, then pick order.    */
+typedef struct hs_alloc_entry {
+  uint32_t    container;
+  const char* type_key;  /* PodDevices key == request k.Type */
+  const char* uuid;
+  int32_t     idx;
+  int32_t     usedmem;
+  int32_t     usedcores;
+} hs_alloc_entry;
+
+/* Per failed node: reason string exactly as common.GenReason renders it
+ * (common/common.go:46-53) or the node-level reason ("NodeInsufficientDevice",
+ * "node unregistered", …).                                                 */
+typedef struct hs_failed_node {
+  const char* node;
+  const char* reason;
+} hs_failed_node;
+
+/* What Scheduler.Filter produces (scheduler.go:1117-1153): the chosen
+ * policy.NodeScore{NodeID, Devices, Score} (policy/node_policy.go:27-33), the
+ * annotation map it patches onto the pod, or FailedNodes.                  */
+typedef struct hs_filter_result {
+  int32_t               status;      /* HS_FIT | HS_NOFIT | HS_PASSTHROUGH | <0 */
+  int32_t               node_index;  /* position in the candidate list      */
+  const char*           node_name;
+  float                 score;
+  const hs_alloc_entry* entries;
+  uint32_t              n_entries;
+  const hs_kv*          annotations; /* without hami.io/vgpu-time / predicate-time values (set to "") */
+  uint32_t              n_annotations;
+  const hs_failed_node* failed;
+  uint32_t              n_failed;
+} hs_filter_result;
+
+/* One row of the usage cache: DeviceUsage{Used, Usedmem, Usedcores}.        */
+typedef struct hs_device_usage_row {
+  int32_t used;
+  int32_t usedmem;
+  int32_t usedcores;
+} hs_device_usage_row;
+
+/* ---- configuration ----------------------------------------------------- */
+
+/* One Ascend VNPUConfig (pkg/device/ascend/device.go VNPUConfig; defaults in
+ * pkg/scheduler/config/config.go:340-460).  Templates are only used to name the
+ * vNPU template in the huawei.com/<word> annotation (ascend/device.go:69-79,221-253). */
+typedef struct hs_ascend_template {
+  const char* name;
+  int64_t     memory;
+} hs_ascend_template;
+
+typedef struct hs_ascend_config {
+  const char*               common_word;        /* "Ascend910B3", "Ascend910C", "Ascend310P", … */
+  int64_t                   memory_allocatable;
+  int64_t                   memory_capacity;
+  const hs_ascend_template* templates;          /* sorted by memory ascending at load, like InitDevices */
+  uint32_t                  n_templates;
+} hs_ascend_config;
+
+/* cmd/scheduler/main.go:70-71 flags + the vendor registry of
+ * pkg/scheduler/config/config.go:107-251.  NVIDIA, DCU and MLU are always
+ * registered; Ascend words as listed.                                       */
+typedef struct hs_config {
+  const char*             node_scheduler_policy;  /* NULL = "binpack" */
+  const char*             gpu_scheduler_policy;   /* NULL = "spread"  */
+  const hs_ascend_config* ascend;
+  uint32_t                n_ascend;
+  uint8_t                 ascend_hami_vnpu_core;  /* VNPUs.HamiVnpuCore global default */
+  int32_t                 cuda_device;            /* ordinal; -1 = current device      */
+  uint32_t                reserve_nodes;          /* initial HBM capacity in nodes (grows on demand) */
+} hs_config;
+
+typedef struct hs_handle hs_handle;
+
+/* Trace operations for hs_run_batch: the pod stream a scheduler sees. */
+enum { HS_OP_FILTER = 0, HS_OP_DELETE = 1 };
+typedef struct hs_op {
+  int32_t       kind;
+  const hs_pod* pod;   /* FILTER: the pod; DELETE: only uid is read */
+} hs_op;
+
+/* ---- entry points ------------------------------------------------------ */
+
+/* Replaces newScheduler + config.InitDevicesWithConfig for this path.
+ * Fails (returns NULL, message via hs_last_error(NULL)) when no CUDA device
+ * is usable: there is no CPU fallback.                                      */
+hs_handle* hs_create(const hs_config* cfg);
+void       hs_destroy(hs_handle* h);
+const char* hs_last_error(const hs_handle* h);
+
+/* nodeManager.addNode / rmNodeDevices (pkg/scheduler/nodes.go:76-148): insert
+ * or replace a node's static inventory.  Usage already committed on devices
+ * whose UUID survives the update is kept.                                   */
+int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node);
+int32_t hs_node_remove(hs_handle* h, const char* name);
+int32_t hs_node_count(const hs_handle* h);
+
+/* podManager.AddPod fed by the informer (scheduler.go:137-171, pods.go:57-97):
+ * add an already-collapsed allocation (restart replay, pods bound elsewhere).
+ * `slots` 0 counts as 1 (scheduler.go:782).                                 */
+int32_t hs_usage_apply(hs_handle* h, const char* pod_uid, const char* node,
+                       const char* uuid, int32_t slots, int32_t usedmem, int32_t usedcores);
+
+/* podManager.DelPod + usage release (scheduler.go:226-253, pods.go:157-167). */
+int32_t hs_pod_delete(hs_handle* h, const char* pod_uid);
+
+/* Scheduler.Filter (scheduler.go:1067): one pod, sweep + select + commit.
+ * node_names == NULL means "every registered node, in registration order";
+ * otherwise the ExtenderArgs.NodeNames candidate list (unknown names fail with
+ * "node unregistered", scheduler.go:846-853).                               */
+int32_t hs_filter(hs_handle* h, const hs_pod* pod,
+                  const char* const* node_names, uint32_t n_names,
+                  hs_filter_result* out);
+
+/* The same decisions for a whole pod stream, committed one at a time ON THE
+ * DEVICE in stream order (a persistent kernel, one grid barrier per decision),
+ * so assignments equal n sequential hs_filter/hs_pod_delete calls.
+ * Candidates are every registered node.  Returns the number of ops run.     */
+int32_t hs_run_batch(hs_handle* h, const hs_op* ops, uint32_t n_ops);
+/* Result i of the last hs_run_batch (DELETE ops yield status HS_OK, no node). */
+int32_t hs_batch_get(hs_handle* h, uint32_t i, hs_filter_result* out);
+
+/* The reference undoes the commit when the annotation PATCH fails
+ * (scheduler.go:1140-1147): podManager.DelPod + quota RmUsage.              */
+int32_t hs_rollback(hs_handle* h, const char* pod_uid);
+
+/* Usage cache dump for one node, rows in device-slot order (metrics / parity;
+ * the reference's equivalent is InspectAllNodesUsage, scheduler.go:630-639). */
+int32_t hs_snapshot_node(hs_handle* h, const char* node, hs_device_usage_row* rows, uint32_t cap);
+
+/* Device time (ms, CUDA events on the engine's stream) and kernel launches of
+ * the last hs_filter / hs_run_batch, for bench.py.                          */
+double   hs_last_device_ms(const hs_handle* h);
+uint64_t hs_launch_count(const hs_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HAMI_SCHED_H_ */

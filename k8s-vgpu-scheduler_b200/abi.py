@@ -1,0 +1,196 @@
+"""ctypes mirror of include/hami_sched.h (the C ABI a cgo shim binds).
+
+Plain data only: builders turn Python dicts into the caller-owned buffers the
+ABI takes, readers turn hs_filter_result back into Python values.  Nothing here
+computes anything; the engine lives in csrc/ (CUDA) behind libhami_sched.so.
+"""
+import ctypes as C
+
+HS_FIT, HS_NOFIT, HS_PASSTHROUGH = 0, 1, 2
+HS_ERR_INVALID, HS_ERR_CUDA, HS_ERR_UNSUPPORTED, HS_ERR_WEIGHTS, HS_ERR_NOTFOUND = -1, -2, -3, -4, -5
+HS_OP_FILTER, HS_OP_DELETE = 0, 1
+
+REASONS = [
+    "CardTypeMismatch", "CardUuidMismatch", "CardTimeSlicingExhausted", "CardComputeUnitsExhausted",
+    "CardInsufficientMemory", "CardInsufficientCore", "CardNotHealth", "CardCordoned", "NumaNotFit",
+    "ExclusiveDeviceAllocateConflict", "CardNotFoundCustomFilterRule", "CardMigTopologyInfeasible",
+    "AllocatedCardsInsufficientRequest", "ResourceQuotaNotFit", "ModeNotFit",
+]
+
+
+class hs_device_info(C.Structure):
+    _fields_ = [("id", C.c_char_p), ("index", C.c_uint32), ("count", C.c_int32), ("devmem", C.c_int32),
+                ("devcore", C.c_int32), ("type", C.c_char_p), ("numa", C.c_int32), ("mode", C.c_char_p),
+                ("health", C.c_uint8), ("vendor", C.c_char_p), ("network_id", C.c_int32)]
+
+
+class hs_node_info(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("devices", C.POINTER(hs_device_info)), ("n_devices", C.c_uint32),
+                ("pair_scores", C.POINTER(C.c_int32)), ("device_cordon", C.c_char_p), ("hami_vnpu_core", C.c_int8)]
+
+
+class hs_container_request(C.Structure):
+    _fields_ = [("key", C.c_char_p), ("type", C.c_char_p), ("nums", C.c_int32), ("memreq", C.c_int32),
+                ("mempct", C.c_int32), ("coresreq", C.c_int32)]
+
+
+class hs_container(C.Structure):
+    _fields_ = [("reqs", C.POINTER(hs_container_request)), ("n_reqs", C.c_uint32)]
+
+
+class hs_kv(C.Structure):
+    _fields_ = [("key", C.c_char_p), ("value", C.c_char_p)]
+
+
+class hs_pod(C.Structure):
+    _fields_ = [("uid", C.c_char_p), ("ns", C.c_char_p), ("name", C.c_char_p),
+                ("annotations", C.POINTER(hs_kv)), ("n_annotations", C.c_uint32),
+                ("containers", C.POINTER(hs_container)), ("n_containers", C.c_uint32), ("n_init", C.c_uint32)]
+
+
+class hs_alloc_entry(C.Structure):
+    _fields_ = [("container", C.c_uint32), ("type_key", C.c_char_p), ("uuid", C.c_char_p),
+                ("idx", C.c_int32), ("usedmem", C.c_int32), ("usedcores", C.c_int32)]
+
+
+class hs_failed_node(C.Structure):
+    _fields_ = [("node", C.c_char_p), ("reason", C.c_char_p)]
+
+
+class hs_filter_result(C.Structure):
+    _fields_ = [("status", C.c_int32), ("node_index", C.c_int32), ("node_name", C.c_char_p), ("score", C.c_float),
+                ("entries", C.POINTER(hs_alloc_entry)), ("n_entries", C.c_uint32),
+                ("annotations", C.POINTER(hs_kv)), ("n_annotations", C.c_uint32),
+                ("failed", C.POINTER(hs_failed_node)), ("n_failed", C.c_uint32)]
+
+
+class hs_device_usage_row(C.Structure):
+    _fields_ = [("used", C.c_int32), ("usedmem", C.c_int32), ("usedcores", C.c_int32)]
+
+
+class hs_ascend_template(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("memory", C.c_int64)]
+
+
+class hs_ascend_config(C.Structure):
+    _fields_ = [("common_word", C.c_char_p), ("memory_allocatable", C.c_int64), ("memory_capacity", C.c_int64),
+                ("templates", C.POINTER(hs_ascend_template)), ("n_templates", C.c_uint32)]
+
+
+class hs_config(C.Structure):
+    _fields_ = [("node_scheduler_policy", C.c_char_p), ("gpu_scheduler_policy", C.c_char_p),
+                ("ascend", C.POINTER(hs_ascend_config)), ("n_ascend", C.c_uint32),
+                ("ascend_hami_vnpu_core", C.c_uint8), ("cuda_device", C.c_int32), ("reserve_nodes", C.c_uint32)]
+
+
+class hs_op(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("pod", C.POINTER(hs_pod))]
+
+
+def _b(s):
+    if s is None:
+        return None
+    return s if isinstance(s, bytes) else str(s).encode()
+
+
+# Ascend VNPU configs of the reference's built-in default device config
+# (pkg/scheduler/config/config.go:340-460): commonWord, allocatable, capacity, templates.
+DEFAULT_ASCEND = [
+    ("Ascend910A", 32768, 32768, [("vir02", 2184), ("vir04", 4369), ("vir08", 8738), ("vir16", 17476)]),
+    ("Ascend910B2", 65536, 65536, [("vir03_1c_8g", 8192), ("vir06_1c_16g", 16384), ("vir12_3c_32g", 32768)]),
+    ("Ascend910B3", 65536, 65536, [("vir05_1c_16g", 16384), ("vir10_3c_32g", 32768)]),
+    ("Ascend910B4", 32768, 32768, [("vir05_1c_8g", 8192), ("vir10_3c_16g", 16384)]),
+    ("Ascend910C", 65536, 65536, []),
+    ("Ascend310P", 21527, 24576, [("vir01", 3072), ("vir02", 6144), ("vir04", 12288)]),
+]
+
+
+def build_config(node_policy=None, gpu_policy=None, ascend=None, ascend_hami_vnpu_core=False,
+                 cuda_device=-1, reserve_nodes=0):
+    keep = []
+    ascend = DEFAULT_ASCEND if ascend is None else ascend
+    arr = (hs_ascend_config * max(1, len(ascend)))()
+    for i, (word, alloc, cap, templates) in enumerate(ascend):
+        t = (hs_ascend_template * max(1, len(templates)))()
+        for j, (name, mem) in enumerate(templates):
+            t[j].name = _b(name)
+            t[j].memory = mem
+        keep.append(t)
+        arr[i].common_word = _b(word)
+        arr[i].memory_allocatable = alloc
+        arr[i].memory_capacity = cap
+        arr[i].templates = t
+        arr[i].n_templates = len(templates)
+    cfg = hs_config(_b(node_policy), _b(gpu_policy), arr, len(ascend), 1 if ascend_hami_vnpu_core else 0,
+                    cuda_device, reserve_nodes)
+    keep.append(arr)
+    return cfg, keep
+
+
+def build_node(node):
+    """node: {"name", "devices": [{id,index,count,devmem,devcore,type,numa,mode,health,vendor,network_id}],
+    "pair_scores": [[int]] | None, "device_cordon": str | None, "hami_vnpu_core": -1|0|1}"""
+    devs = node["devices"]
+    arr = (hs_device_info * max(1, len(devs)))()
+    for i, d in enumerate(devs):
+        arr[i] = hs_device_info(_b(d["id"]), d.get("index", i), d.get("count", 0), d.get("devmem", 0),
+                                d.get("devcore", 0), _b(d.get("type", "")), d.get("numa", 0), _b(d.get("mode", "")),
+                                1 if d.get("health", True) else 0, _b(d.get("vendor", "NVIDIA")),
+                                d.get("network_id", -1))
+    ps = None
+    keep = [arr]
+    if node.get("pair_scores") is not None:
+        n = len(devs)
+        flat = (C.c_int32 * max(1, n * n))()
+        for i in range(n):
+            for j in range(n):
+                flat[i * n + j] = int(node["pair_scores"][i][j])
+        ps = C.cast(flat, C.POINTER(C.c_int32))
+        keep.append(flat)
+    ni = hs_node_info(_b(node["name"]), arr, len(devs), ps, _b(node.get("device_cordon")),
+                      node.get("hami_vnpu_core", -1))
+    return ni, keep
+
+
+def build_pod(pod):
+    """pod: {"uid","ns","name","annotations": {k: v}, "containers": [[{key,type,nums,memreq,mempct,coresreq}]], "n_init"}"""
+    keep = []
+    annos = pod.get("annotations") or {}
+    kv = (hs_kv * max(1, len(annos)))()
+    for i, (k, v) in enumerate(annos.items()):
+        kv[i] = hs_kv(_b(k), _b(v))
+    ctrs = pod.get("containers") or []
+    carr = (hs_container * max(1, len(ctrs)))()
+    for i, reqs in enumerate(ctrs):
+        rarr = (hs_container_request * max(1, len(reqs)))()
+        for j, r in enumerate(reqs):
+            rarr[j] = hs_container_request(_b(r.get("key", r["type"])), _b(r["type"]), r.get("nums", 0),
+                                           r.get("memreq", 0), r.get("mempct", 0), r.get("coresreq", 0))
+        keep.append(rarr)
+        carr[i] = hs_container(rarr, len(reqs))
+    keep += [kv, carr]
+    p = hs_pod(_b(pod.get("uid", pod.get("name", ""))), _b(pod.get("ns", "default")), _b(pod.get("name", "")),
+               kv, len(annos), carr, len(ctrs), pod.get("n_init", 0))
+    return p, keep
+
+
+def _s(p):
+    return p.decode() if p is not None else None
+
+
+def read_result(res):
+    """hs_filter_result -> dict. devices: {type_key: [[(uuid, idx, usedmem, usedcores), ...] per container]}"""
+    out = {"status": res.status, "node_index": res.node_index, "node": _s(res.node_name), "score": res.score,
+           "devices": {}, "annotations": {}, "failed": {}}
+    for i in range(res.n_entries):
+        e = res.entries[i]
+        lst = out["devices"].setdefault(_s(e.type_key), [])
+        while len(lst) <= e.container:
+            lst.append([])
+        if e.uuid is not None:
+            lst[e.container].append((_s(e.uuid), e.idx, e.usedmem, e.usedcores))
+    for i in range(res.n_annotations):
+        out["annotations"][_s(res.annotations[i].key)] = _s(res.annotations[i].value)
+    for i in range(res.n_failed):
+        out["failed"][_s(res.failed[i].node)] = _s(res.failed[i].reason)
+    return out

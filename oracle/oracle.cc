@@ -1,0 +1,1116 @@
+// oracle.cc — TEST INFRASTRUCTURE ONLY (see oracle.h for scope, status and the
+// canonical linearisation rules).  CPU restatement of the reference's
+// Filter/Score path; every function cites the reference file:line it follows.
+// Build with -ffp-contract=off: Go/amd64 rounds every float32 op separately.
+#include "oracle.h"
+
+#include <algorithm>
+#include <cassert>
+#include <cstdio>
+#include <cstring>
+#include <set>
+#include <stdexcept>
+#include <thread>
+
+namespace oracle {
+
+// ---------------------------------------------------------------------------
+// Go-semantics helpers
+// ---------------------------------------------------------------------------
+static inline int32_t i32add(int32_t a, int32_t b) { return (int32_t)((uint32_t)a + (uint32_t)b); }
+static inline int32_t i32sub(int32_t a, int32_t b) { return (int32_t)((uint32_t)a - (uint32_t)b); }
+static inline int32_t i32mul(int32_t a, int32_t b) { return (int32_t)((uint32_t)a * (uint32_t)b); }
+
+static bool isSpace(unsigned char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\v' || c == '\f' || c == '\r'; }
+static std::string TrimSpace(const std::string& s) {  // strings.TrimSpace (ASCII subset)
+  size_t a = 0, b = s.size();
+  while (a < b && isSpace((unsigned char)s[a])) a++;
+  while (b > a && isSpace((unsigned char)s[b - 1])) b--;
+  return s.substr(a, b - a);
+}
+static std::vector<std::string> Split(const std::string& s, char sep) {  // strings.Split
+  std::vector<std::string> out;
+  size_t start = 0;
+  for (;;) {
+    size_t p = s.find(sep, start);
+    if (p == std::string::npos) { out.push_back(s.substr(start)); break; }
+    out.push_back(s.substr(start, p - start));
+    start = p + 1;
+  }
+  return out;
+}
+static std::string ToUpper(std::string s) { for (auto& c : s) if (c >= 'a' && c <= 'z') c = (char)(c - 32); return s; }
+static std::string ToLower(std::string s) { for (auto& c : s) if (c >= 'A' && c <= 'Z') c = (char)(c + 32); return s; }
+static bool Contains(const std::string& s, const std::string& sub) { return s.find(sub) != std::string::npos; }
+static bool HasPrefix(const std::string& s, const std::string& p) { return s.compare(0, p.size(), p) == 0; }
+static bool ParseBool(const std::string& s, bool& v) {  // strconv.ParseBool
+  static const char* T[] = {"1", "t", "T", "TRUE", "true", "True"};
+  static const char* F[] = {"0", "f", "F", "FALSE", "false", "False"};
+  for (auto t : T) if (s == t) { v = true; return true; }
+  for (auto f : F) if (s == f) { v = false; return true; }
+  return false;
+}
+static const std::string* anno(const Pod& pod, const std::string& key) {
+  auto it = pod.Annotations.find(key);
+  return it == pod.Annotations.end() ? nullptr : &it->second;
+}
+
+// ---------------------------------------------------------------------------
+// pkg/device/common/common.go:46-53
+// ---------------------------------------------------------------------------
+std::string GenReason(const std::map<std::string, int>& reasons, int cards) {
+  std::vector<std::string> reason;
+  for (auto& kv : reasons) {
+    char buf[160];
+    snprintf(buf, sizeof buf, "%d/%d %s", kv.second, cards, kv.first.c_str());
+    reason.push_back(buf);
+  }
+  std::sort(reason.begin(), reason.end());
+  std::string out;
+  for (size_t i = 0; i < reason.size(); i++) { if (i) out += ", "; out += reason[i]; }
+  return out;
+}
+
+// ---------------------------------------------------------------------------
+// pkg/device/devices.go:693-738
+// ---------------------------------------------------------------------------
+bool CheckUUID(const std::map<std::string, std::string>& annos, const std::string& id,
+               const std::string& useKey, const std::string& noUseKey) {
+  auto match = [&](const std::string& list) {
+    for (auto& u : Split(list, ',')) if (TrimSpace(u) == id) return true;
+    return false;
+  };
+  auto it = annos.find(useKey);
+  if (it != annos.end() && TrimSpace(it->second) != "") {
+    if (!match(it->second)) return false;
+  }
+  it = annos.find(noUseKey);
+  if (it != annos.end() && TrimSpace(it->second) != "") {
+    if (match(it->second)) return false;
+  }
+  return true;
+}
+
+bool CheckType(const std::map<std::string, std::string>& annos, const std::string& cardTypeIn,
+               const std::string& useKey, const std::string& noUseKey) {
+  std::string cardType = ToUpper(cardTypeIn);
+  auto match = [&](const std::string& list) {
+    for (auto& t0 : Split(list, ',')) {
+      std::string t = TrimSpace(t0);
+      if (t != "" && Contains(cardType, ToUpper(t))) return true;
+    }
+    return false;
+  };
+  auto it = annos.find(useKey);
+  if (it != annos.end() && TrimSpace(it->second) != "") {
+    if (!match(it->second)) return false;
+  }
+  it = annos.find(noUseKey);
+  if (it != annos.end() && TrimSpace(it->second) != "") {
+    if (match(it->second)) return false;
+  }
+  return true;
+}
+
+// pkg/util/util.go:277-298
+std::string GetGPUSchedulerPolicyByPod(const std::string& def, const Pod& pod) {
+  if (auto v = anno(pod, "hami.io/gpu-scheduler-policy")) return *v;
+  return def;
+}
+bool PolicyContains(const std::string& policy, const std::string& name) {
+  for (auto& p : Split(policy, ',')) if (TrimSpace(p) == name) return true;
+  return false;
+}
+
+// pkg/util/device_scoring_weights.go:58-102
+bool ParseDeviceScoringWeights(const std::string& value, DeviceScoringWeights& weights, std::string& err) {
+  weights = DeviceScoringWeights{0, 0, 0};
+  std::set<std::string> seen;
+  auto parts = Split(value, ',');
+  if (parts.size() != 3) { err = "expected slot, core, and memory weights"; return false; }
+  for (auto& part : parts) {
+    std::string p = TrimSpace(part);
+    size_t eq = p.find('=');
+    if (eq == std::string::npos) { err = "expected key=value entries"; return false; }
+    std::string key = TrimSpace(p.substr(0, eq));
+    std::string val = TrimSpace(p.substr(eq + 1));
+    if (seen.count(key)) { err = "duplicate weight"; return false; }
+    // strconv.ParseInt(val, 10, 64)
+    if (val.empty()) { err = "weight must be an integer"; return false; }
+    size_t i = 0; bool neg = false;
+    if (val[0] == '+' || val[0] == '-') { neg = val[0] == '-'; i = 1; }
+    if (i >= val.size()) { err = "weight must be an integer"; return false; }
+    unsigned long long acc = 0;
+    for (; i < val.size(); i++) {
+      if (val[i] < '0' || val[i] > '9') { err = "weight must be an integer"; return false; }
+      unsigned long long d = (unsigned long long)(val[i] - '0');
+      if (acc > (0x8000000000000000ULL - d) / 10) { err = "weight must be an integer"; return false; }
+      acc = acc * 10 + d;
+    }
+    if (!neg && acc > 0x7fffffffffffffffULL) { err = "weight must be an integer"; return false; }
+    int64_t w = neg ? (int64_t)(0 - acc) : (int64_t)acc;
+    if (w < 0) { err = "weight must not be negative"; return false; }
+    if (key == "slot") weights.Slot = w;
+    else if (key == "core") weights.Core = w;
+    else if (key == "memory") weights.Memory = w;
+    else { err = "unknown weight"; return false; }
+    seen.insert(key);
+  }
+  if (weights.Slot == 0 && weights.Core == 0 && weights.Memory == 0) { err = "at least one weight must be positive"; return false; }
+  return true;
+}
+
+// ---------------------------------------------------------------------------
+// pkg/scheduler/policy/gpu_policy.go
+// ---------------------------------------------------------------------------
+// gpu_policy.go:194-222
+void DeviceListsScore::ComputeScore(const ContainerDeviceRequests& requests, const DeviceScoringWeights& weights) {
+  if (Device.Count == 0 || Device.Totalcore == 0 || Device.Totalmem == 0) { Score = 0; return; }
+  int32_t request = 0, core = 0, mem = 0;
+  for (auto& kv : requests) {
+    const ContainerDeviceRequest& container = kv.second;
+    if (container.Type != Device.Type) continue;
+    request = i32add(request, 1);
+    core = i32add(core, container.Coresreq);
+    if (container.MemPercentagereq != 0 && container.MemPercentagereq != 101) {
+      mem = i32add(mem, (int32_t)(((int64_t)Device.Totalmem * (int64_t)container.MemPercentagereq) / 100));
+      continue;
+    }
+    mem = i32add(mem, container.Memreq);
+  }
+  float usedScore = (float)i32add(request, Device.Used) / (float)Device.Count;
+  float coreScore = (float)i32add(core, Device.Usedcores) / (float)Device.Totalcore;
+  float memScore = (float)i32add(mem, Device.Usedmem) / (float)Device.Totalmem;
+  float a = (float)weights.Slot * usedScore;
+  float b = (float)weights.Core * coreScore;
+  float c = (float)weights.Memory * memScore;
+  float s = a + b;
+  s = s + c;
+  Score = (float)10 * s;
+}
+
+// gpu_policy.go:62-75
+static std::vector<std::string> gpuSortKeyChain(const std::string& policy) {
+  static const char* order[] = {"binpack", "spread", "numa"};
+  std::set<std::string> seen;
+  std::vector<std::string> chain;
+  for (auto& p : Split(policy, ',')) {
+    std::string name = TrimSpace(p);
+    for (auto key : order) {
+      if (name == key && !seen.count(key)) { chain.push_back(key); seen.insert(key); }
+    }
+  }
+  return chain;
+}
+
+// gpu_policy.go:77-167
+bool DeviceUsageList::Less(int i, int j) const {
+  const DeviceListsScore& a = DeviceLists[i];
+  const DeviceListsScore& b = DeviceLists[j];
+  if (Contains(Policy, ",") || Policy == "numa") {
+    // lessByChain, gpu_policy.go:132-167
+    std::vector<std::string> chain = gpuSortKeyChain(Policy);
+    if (chain.empty()) chain = {"spread"};
+    if (NumaBind && chain[0] != "numa") {
+      std::vector<std::string> withNuma = {"numa"};
+      for (auto& key : chain) if (key != "numa") withNuma.push_back(key);
+      chain = withNuma;
+    }
+    for (auto& key : chain) {
+      if (key == "binpack") { if (a.Score != b.Score) return a.Score < b.Score; }
+      else if (key == "spread") { if (a.Score != b.Score) return a.Score > b.Score; }
+      else if (key == "numa") { if (a.Device.Numa != b.Device.Numa) return a.Device.Numa < b.Device.Numa; }
+    }
+    return a.Device.Index < b.Device.Index;
+  }
+  float si = a.Score, sj = b.Score;
+  int ni = a.Device.Numa, nj = b.Device.Numa;
+  bool binpack = Policy == "binpack";
+  if (Policy == "mutex") {
+    int32_t ui = a.Device.Used, uj = b.Device.Used;
+    if (ui != uj) return ui > uj;
+    return ni < nj;
+  }
+  if (NumaBind) {
+    if (binpack) {
+      if (ni == nj) return si < sj;
+      return ni > nj;
+    }
+    if (ni == nj) return si > sj;
+    return ni < nj;
+  }
+  if (binpack) {
+    if (si != sj) return si < sj;
+    return ni < nj;
+  }
+  if (si != sj) return si > sj;
+  return ni < nj;
+}
+
+// Go's sort.Sort → pdqsort; for n <= 12 it is insertionSort (stable):
+//   for i := a+1; i < b; i++ { for j := i; j > a && Less(j, j-1); j-- { Swap(j, j-1) } }
+void DeviceUsageList::Sort() {
+  int n = (int)DeviceLists.size();
+  if (n > 12) throw std::runtime_error("oracle: >12 devices per node (canonical rule 5)");
+  for (int i = 1; i < n; i++)
+    for (int j = i; j > 0 && Less(j, j - 1); j--) std::swap(DeviceLists[j], DeviceLists[j - 1]);
+}
+
+// ---------------------------------------------------------------------------
+// pkg/scheduler/policy/node_policy.go:106-130
+// ---------------------------------------------------------------------------
+float ComputeDefaultScore(const DeviceUsageList& devices) {
+  int32_t used = 0, usedCore = 0, usedMem = 0;
+  for (auto& d : devices.DeviceLists) {
+    used = i32add(used, d.Device.Used);
+    usedCore = i32add(usedCore, d.Device.Usedcores);
+    usedMem = i32add(usedMem, d.Device.Usedmem);
+  }
+  int32_t total = 0, totalCore = 0, totalMem = 0;
+  for (auto& d : devices.DeviceLists) {
+    total = i32add(total, d.Device.Count);
+    totalCore = i32add(totalCore, d.Device.Totalcore);
+    totalMem = i32add(totalMem, d.Device.Totalmem);
+  }
+  if (total == 0 || totalCore == 0 || totalMem == 0) return 0;
+  float useScore = (float)used / (float)total;
+  float coreScore = (float)usedCore / (float)totalCore;
+  float memScore = (float)usedMem / (float)totalMem;
+  float s = useScore + coreScore;
+  s = s + memScore;
+  return (float)10 * s;
+}
+
+// ---------------------------------------------------------------------------
+// pkg/device/initContainer.go:36-114
+// ---------------------------------------------------------------------------
+PodDevices CollapseInitContainerUsage(int numInit, const PodDevices& raw) {
+  struct usage { int32_t mem = 0, cores = 0, slots = 0; };
+  std::map<std::pair<std::string, std::string>, usage> initPeak, appSum;
+  for (auto& kv : raw) {
+    const std::string& devType = kv.first;
+    for (size_t cidx = 0; cidx < kv.second.size(); cidx++) {
+      for (auto& dev : kv.second[cidx]) {
+        auto key = std::make_pair(devType, dev.UUID);
+        if ((int)cidx < numInit) {
+          usage& cur = initPeak[key];
+          if (dev.Usedmem > cur.mem) cur.mem = dev.Usedmem;
+          if (dev.Usedcores > cur.cores) cur.cores = dev.Usedcores;
+          cur.slots = 1;
+        } else {
+          usage& cur = appSum[key];
+          cur.mem = i32add(cur.mem, dev.Usedmem);
+          cur.cores = i32add(cur.cores, dev.Usedcores);
+          cur.slots++;
+        }
+      }
+    }
+  }
+  PodDevices collapsed;
+  for (auto& kv : raw) {
+    const std::string& devType = kv.first;
+    std::set<std::string> uuidSet;
+    for (auto& k : initPeak) if (k.first.first == devType) uuidSet.insert(k.first.second);
+    for (auto& k : appSum) if (k.first.first == devType) uuidSet.insert(k.first.second);
+    ContainerDevices containerDevs;
+    for (auto& uuid : uuidSet) {  // std::set iterates sorted == the reference's sort.Slice by UUID
+      usage initU, appU;
+      auto a = initPeak.find({devType, uuid});
+      if (a != initPeak.end()) initU = a->second;
+      auto b = appSum.find({devType, uuid});
+      if (b != appSum.end()) appU = b->second;
+      ContainerDevice cd;
+      cd.UUID = uuid;
+      cd.Type = devType;
+      cd.Usedmem = std::max(initU.mem, appU.mem);
+      cd.Usedcores = std::max(initU.cores, appU.cores);
+      cd.Slots = std::max(std::max(initU.slots, appU.slots), 1);
+      containerDevs.push_back(cd);
+    }
+    collapsed[devType] = PodSingleDevice{containerDevs};
+  }
+  return collapsed;
+}
+
+// pkg/device/devices.go:451-484
+static std::string EncodeContainerDevices(const ContainerDevices& cd) {
+  std::string s;
+  for (auto& val : cd) {
+    s += val.UUID + "," + val.Type + "," + std::to_string(val.Usedmem) + "," + std::to_string(val.Usedcores) + ":";
+  }
+  return s;
+}
+std::string EncodePodSingleDevice(const PodSingleDevice& pd) {
+  std::string res;
+  for (auto& ctrdevs : pd) { res += EncodeContainerDevices(ctrdevs); res += ";"; }
+  return res;
+}
+
+// ---------------------------------------------------------------------------
+// Vendor Fit — the shared template.  nvidia/device.go:715-876, hygon/device.go:264-369,
+// cambricon/device.go:378-488, ascend/device.go:442-617 are one loop with
+// per-vendor gates; the gates are spelled out per vendor below.
+// ---------------------------------------------------------------------------
+void Devices::AddResourceUsage(DeviceUsage& n, const ContainerDevice& ctr) const {
+  // nvidia/device.go:645-664 (non-MIG), hygon:257, cambricon:338, ascend:426
+  n.Used = i32add(n.Used, 1);
+  n.Usedcores = i32add(n.Usedcores, ctr.Usedcores);
+  n.Usedmem = i32add(n.Usedmem, ctr.Usedmem);
+}
+
+namespace {
+
+enum class Vendor { NVIDIA, DCU, MLU, ASCEND };
+
+struct FitGates {
+  Vendor vendor;
+  std::string commonWord;
+  std::string useType, noUseType;   // type selector annotation keys ("" = none)
+  std::string useUUID, noUseUUID;
+  bool ascendHamiVnpuCoreDefault = false;
+};
+
+// generateCombinations, nvidia/device.go:887-915 (lexicographic index order)
+void combos(const ContainerDevices& arr, int start, int k, ContainerDevices& cur, std::vector<ContainerDevices>& out) {
+  if (k == 0) { out.push_back(cur); return; }
+  for (int i = start; i <= (int)arr.size() - k; i++) {
+    cur.push_back(arr[i]);
+    combos(arr, i + 1, k - 1, cur, out);
+    cur.pop_back();
+  }
+}
+
+int pairScore(const NodeInfo* nodeInfo, const std::string& a, const std::string& b) {
+  // getDevicePairScoreMap, nvidia/device.go:917-925; missing entries read as 0 (Go map zero value)
+  if (!nodeInfo) return 0;
+  auto it = nodeInfo->Devices.find("NVIDIA");
+  if (it == nodeInfo->Devices.end()) return 0;
+  for (auto& d : it->second) {
+    if (d.ID == a) {
+      auto s = d.PairScores.find(b);
+      return s == d.PairScores.end() ? 0 : s->second;
+    }
+  }
+  return 0;
+}
+
+// computeWorstSingleCard, nvidia/device.go:927-951
+ContainerDevices computeWorstSingleCard(const NodeInfo* nodeInfo, const ContainerDevices& devices) {
+  int worstScore = 0;
+  ContainerDevices worst;
+  bool found = false;
+  for (auto& dev1 : devices) {
+    int total = 0;
+    for (auto& dev2 : devices) {
+      if (dev1.UUID == dev2.UUID) continue;
+      total += pairScore(nodeInfo, dev1.UUID, dev2.UUID);
+    }
+    if (!found || total < worstScore) { found = true; worstScore = total; worst = ContainerDevices{dev1}; }
+  }
+  return worst;
+}
+
+// computeBestCombination, nvidia/device.go:953-978
+ContainerDevices computeBestCombination(const NodeInfo* nodeInfo, const std::vector<ContainerDevices>& combinations) {
+  int bestScore = -1;
+  ContainerDevices best;
+  bool found = false;
+  for (auto& partition : combinations) {
+    int total = 0;
+    for (size_t i = 0; i + 1 < partition.size(); i++)
+      for (size_t z = i + 1; z < partition.size(); z++)
+        total += pairScore(nodeInfo, partition[i].UUID, partition[z].UUID);
+    if (!found || total > bestScore) { found = true; bestScore = total; best = partition; }
+  }
+  return best;
+}
+
+// ascend/device.go:631-675 (canonical rule 7 for equal counts)
+ContainerDevices ascendBestCombination(int reqNum, const ContainerDevices& containerDevices) {
+  std::map<int, ContainerDevices> networkDeviceMap;
+  for (auto& cd : containerDevices)
+    if (cd.HasNetworkID) networkDeviceMap[cd.NetworkID].push_back(cd);
+  std::vector<std::pair<int, int>> sortedNetworks;  // (NetworkID, Count), ascending NetworkID from std::map
+  for (auto& kv : networkDeviceMap) sortedNetworks.push_back({kv.first, (int)kv.second.size()});
+  std::stable_sort(sortedNetworks.begin(), sortedNetworks.end(),
+                   [](const std::pair<int, int>& a, const std::pair<int, int>& b) { return a.second > b.second; });
+  ContainerDevices result;
+  for (auto& item : sortedNetworks) {
+    for (auto& dev : networkDeviceMap[item.first]) {
+      result.push_back(dev);
+      if ((int)result.size() == reqNum) return result;
+    }
+  }
+  return result;
+}
+
+// ascend/device.go:677-733 (canonical rule 7 for equal sizes)
+ContainerDevices ascendBestCombination910C(int reqNum, const ContainerDevices& containerDevices) {
+  std::map<int, ContainerDevice> indexToDevice;
+  std::vector<int> npuIndices;
+  for (auto& dev : containerDevices) { indexToDevice[dev.Idx] = dev; npuIndices.push_back(dev.Idx); }
+  const int MaxCardNPUNum = 2;
+  std::map<int, std::vector<int>> cardTopology;  // ascending card id
+  for (int idx : npuIndices) cardTopology[idx / MaxCardNPUNum].push_back(idx);
+  std::vector<std::vector<int>> cardTopSlice;
+  for (auto& kv : cardTopology) cardTopSlice.push_back(kv.second);
+  std::stable_sort(cardTopSlice.begin(), cardTopSlice.end(),
+                   [](const std::vector<int>& a, const std::vector<int>& b) { return a.size() > b.size(); });
+  std::vector<int> selected;
+  int taskNPUNum = reqNum;
+  for (auto& card : cardTopSlice) {
+    if (taskNPUNum <= 0) break;
+    if ((int)card.size() == MaxCardNPUNum) {
+      selected.insert(selected.end(), card.begin(), card.end());
+      taskNPUNum -= MaxCardNPUNum;
+    }
+  }
+  ContainerDevices result;
+  for (int idx : selected) {
+    auto it = indexToDevice.find(idx);
+    if (it != indexToDevice.end()) result.push_back(it->second);
+  }
+  return result;
+}
+
+FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request,
+                      const Pod& pod, const NodeInfo* nodeInfo, const std::string& gpuPolicyDefault) {
+  ContainerDeviceRequest k = request;
+  int32_t originReq = k.Nums;
+  int prevnuma = -1;
+  ContainerDevices tmpDevs;
+  std::map<std::string, int> reason;
+  std::string gpuPolicy = GetGPUSchedulerPolicyByPod(gpuPolicyDefault, pod);
+  bool isMutex = PolicyContains(gpuPolicy, "mutex");
+  bool needTopology = false;
+  bool isHAMiCore = false;
+
+  std::set<std::string> cordoned;
+  if (g.vendor == Vendor::NVIDIA) {
+    needTopology = PolicyContains(gpuPolicy, "topology-aware");  // nvidia/device.go:724
+    // cordonedDevices, nvidia/device.go:698-713
+    if (nodeInfo && nodeInfo->DeviceCordon && TrimSpace(*nodeInfo->DeviceCordon) != "") {
+      for (auto& u0 : Split(*nodeInfo->DeviceCordon, ',')) {
+        std::string u = TrimSpace(u0);
+        if (u != "") cordoned.insert(u);
+      }
+    }
+  }
+  if (g.vendor == Vendor::ASCEND) {
+    // ascend/device.go:452-480
+    std::string vnpuMode;
+    if (auto v = anno(pod, "huawei.com/vnpu-mode")) vnpuMode = *v;
+    isHAMiCore = vnpuMode == "hami-core";
+    bool nodeSupportHamiCore = g.ascendHamiVnpuCoreDefault;
+    if (nodeInfo && nodeInfo->HamiVnpuCore) nodeSupportHamiCore = *nodeInfo->HamiVnpuCore == "true";
+    if (isHAMiCore && !nodeSupportHamiCore) {
+      reason["ModeNotFit"]++;
+      FitResult r; r.fit = false; r.reason = GenReason(reason, (int)devices.size());
+      return r;
+    }
+    if (HasPrefix(g.commonWord, "Ascend910")) {
+      bool all = true;  // hasNetworkID, ascend/device.go:619-629
+      for (auto d : devices) if (!d->HasNetworkID) { all = false; break; }
+      if (all) needTopology = true;
+    }
+  }
+  const bool is910CMulti = g.vendor == Vendor::ASCEND && k.Type == "Ascend910C" && originReq > 1;
+
+  for (int i = (int)devices.size() - 1; i >= 0; i--) {
+    DeviceUsage* dev = devices[i];
+    if (!dev->Health) { reason["CardNotHealth"]++; continue; }
+    if (g.vendor == Vendor::NVIDIA && cordoned.count(dev->ID)) { reason["CardCordoned"]++; continue; }
+    // checkType: nvidia/device.go:493-503, hygon:161-166, cambricon:250-255, ascend:303-308
+    bool found = false, numa = false;
+    if (k.Type == g.commonWord) {
+      switch (g.vendor) {
+        case Vendor::NVIDIA: {
+          bool typeCheck = CheckType(pod.Annotations, dev->Type, g.useType, g.noUseType);
+          if (auto mode = anno(pod, "nvidia.com/vgpu-mode")) {
+            if (!Contains(*mode, dev->Mode)) typeCheck = false;
+          }
+          found = typeCheck;
+          bool enforce = false;  // assertNuma, nvidia/device.go:482-491
+          if (auto nb = anno(pod, "nvidia.com/numa-bind")) { bool v; if (ParseBool(*nb, v) && v) enforce = true; }
+          numa = enforce;
+          break;
+        }
+        case Vendor::DCU:
+          found = CheckType(pod.Annotations, dev->Type, g.useType, g.noUseType);
+          break;
+        case Vendor::MLU:
+        case Vendor::ASCEND:
+          found = true;
+          break;
+      }
+    }
+    if (!found) { reason["CardTypeMismatch"]++; continue; }
+    if (numa && prevnuma != dev->Numa) {
+      if (k.Nums != originReq) reason["NumaNotFit"] += (int)tmpDevs.size();
+      k.Nums = originReq;
+      prevnuma = dev->Numa;
+      tmpDevs.clear();
+    }
+    if (!CheckUUID(pod.Annotations, dev->ID, g.useUUID, g.noUseUUID)) { reason["CardUuidMismatch"]++; continue; }
+
+    int32_t memreq = 0;
+    if (dev->Count <= dev->Used) { reason["CardTimeSlicingExhausted"]++; continue; }
+    if (isMutex && dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+    if (k.Coresreq > 100) k.Coresreq = 100;
+    if (k.Memreq > 0) memreq = k.Memreq;
+    if (k.MemPercentagereq != 101 && k.Memreq == 0) memreq = i32mul(dev->Totalmem, k.MemPercentagereq) / 100;
+    // fitQuota (nvidia/device.go:784, cambricon/device.go:439): the namespace has no quota entry → true (quota.go:73-76)
+    if (i32sub(dev->Totalmem, dev->Usedmem) < memreq) { reason["CardInsufficientMemory"]++; continue; }
+    int32_t effectiveTotalCore = dev->Totalcore;
+    if (isHAMiCore) effectiveTotalCore = 100;  // ascend/device.go:540-543
+    if (i32sub(effectiveTotalCore, dev->Usedcores) < k.Coresreq) { reason["CardInsufficientCore"]++; continue; }
+    if (effectiveTotalCore == 100 && k.Coresreq == 100 && dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+    if (effectiveTotalCore != 0 && dev->Usedcores == effectiveTotalCore && k.Coresreq == 0) { reason["CardComputeUnitsExhausted"]++; continue; }
+    if (g.vendor == Vendor::NVIDIA && dev->Mode == "mig")
+      throw std::runtime_error("oracle: MIG devices are outside the restated scope");
+
+    bool decrement;
+    if (g.vendor == Vendor::NVIDIA) decrement = !needTopology;                               // nvidia/device.go:831-833
+    else if (g.vendor == Vendor::ASCEND) decrement = !needTopology && !is910CMulti;          // ascend/device.go:564
+    else decrement = true;
+    if (k.Nums > 0) {
+      if (decrement) k.Nums--;
+      ContainerDevice cd;
+      cd.Idx = (int)dev->Index;
+      cd.UUID = dev->ID;
+      cd.Type = k.Type;
+      cd.Usedmem = memreq;
+      cd.Usedcores = k.Coresreq;
+      if (g.vendor == Vendor::ASCEND) { cd.HasNetworkID = dev->HasNetworkID; cd.NetworkID = dev->NetworkID; }
+      tmpDevs.push_back(cd);
+    }
+    if (k.Nums == 0 && decrement) {
+      FitResult r; r.fit = true; r.devs = tmpDevs;
+      return r;
+    }
+  }
+
+  if (is910CMulti) {  // ascend/device.go:582-593
+    ContainerDevices combination = ascendBestCombination910C((int)originReq, tmpDevs);
+    if ((int)combination.size() != (int)originReq) {
+      reason["AllocatedCardsInsufficientRequest"] = (int)combination.size();
+      FitResult r; r.fit = false; r.devs = tmpDevs; r.reason = GenReason(reason, (int)originReq);
+      return r;
+    }
+    FitResult r; r.fit = true; r.devs = combination;
+    return r;
+  }
+  if (needTopology) {
+    if ((int)tmpDevs.size() == (int)originReq) { FitResult r; r.fit = true; r.devs = tmpDevs; return r; }
+    if ((int)tmpDevs.size() > (int)originReq) {
+      FitResult r; r.fit = true;
+      if (g.vendor == Vendor::NVIDIA) {  // nvidia/device.go:855-868
+        if (originReq == 1) r.devs = computeWorstSingleCard(nodeInfo, tmpDevs);
+        else {
+          std::vector<ContainerDevices> combinations;
+          ContainerDevices cur;
+          combos(tmpDevs, 0, (int)request.Nums, cur, combinations);
+          r.devs = computeBestCombination(nodeInfo, combinations);
+        }
+      } else {  // ascend/device.go:599-607
+        if (originReq == 1) r.devs = ContainerDevices{tmpDevs[0]};
+        else r.devs = ascendBestCombination((int)originReq, tmpDevs);
+      }
+      return r;
+    }
+  }
+  if (!tmpDevs.empty()) reason["AllocatedCardsInsufficientRequest"] = (int)tmpDevs.size();
+  FitResult r; r.fit = false; r.devs = tmpDevs; r.reason = GenReason(reason, (int)devices.size());
+  return r;
+}
+
+class NvidiaGPUDevices : public Devices {
+ public:
+  std::string CommonWord() const override { return "NVIDIA"; }
+  FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
+                const NodeInfo* nodeInfo, const std::string& def) const override {
+    FitGates g{Vendor::NVIDIA, "NVIDIA", "nvidia.com/use-gputype", "nvidia.com/nouse-gputype",
+               "nvidia.com/use-gpuuuid", "nvidia.com/nouse-gpuuuid"};
+    return fitTemplate(g, devices, request, pod, nodeInfo, def);
+  }
+  void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
+    // nvidia/device.go:505-518
+    auto it = pd.find("NVIDIA");
+    if (it != pd.end() && !it->second.empty()) {
+      std::string s = EncodePodSingleDevice(it->second);
+      annos["hami.io/vgpu-devices-to-allocate"] = s;
+      annos["hami.io/vgpu-devices-allocated"] = s;
+    }
+  }
+};
+
+class DCUDevices : public Devices {
+ public:
+  std::string CommonWord() const override { return "DCU"; }
+  FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
+                const NodeInfo* nodeInfo, const std::string& def) const override {
+    FitGates g{Vendor::DCU, "DCU", "hygon.com/use-dcutype", "hygon.com/nouse-dcutype",
+               "hygon.com/use-gpuuuid", "hygon.com/nouse-gpuuuid"};
+    return fitTemplate(g, devices, request, pod, nodeInfo, def);
+  }
+  void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
+    // hygon/device.go:241-251
+    auto it = pd.find("DCU");
+    if (it != pd.end() && !it->second.empty()) {
+      std::string s = EncodePodSingleDevice(it->second);
+      annos["hami.io/dcu-devices-to-allocate"] = s;
+      annos["hami.io/dcu-devices-allocated"] = s;
+    }
+  }
+};
+
+class CambriconDevices : public Devices {
+ public:
+  std::string CommonWord() const override { return "MLU"; }
+  FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
+                const NodeInfo* nodeInfo, const std::string& def) const override {
+    FitGates g{Vendor::MLU, "MLU", "", "", "cambricon.com/use-gpuuuid", "cambricon.com/nouse-gpuuuid"};
+    return fitTemplate(g, devices, request, pod, nodeInfo, def);
+  }
+  void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
+    // cambricon/device.go:312-332
+    auto it = pd.find("MLU");
+    if (it != pd.end() && !it->second.empty()) {
+      annos["CAMBRICON_DSMLU_ASSIGNED"] = "false";
+      for (auto& ctrdevs : it->second) {
+        if (!ctrdevs.empty()) {
+          const ContainerDevice& d = ctrdevs[0];
+          annos["CAMBRICON_DSMLU_PROFILE"] = std::to_string(d.Idx) + "_" + std::to_string(d.Usedcores) + "_" + std::to_string(d.Usedmem / 256);
+          break;
+        }
+      }
+      std::string s = EncodePodSingleDevice(it->second);
+      annos["hami.io/cambricon-mlu-devices-to-allocate"] = s;
+      annos["hami.io/cambricon-mlu-devices-allocated"] = s;
+    }
+  }
+};
+
+class AscendDevices : public Devices {
+ public:
+  AscendDevices(const AscendConfig& c, bool hamiVnpuCore) : cfg_(c), hamiVnpuCore_(hamiVnpuCore) {
+    // InitDevices sorts templates by memory, ascend/device.go:98-100
+    std::stable_sort(cfg_.Templates.begin(), cfg_.Templates.end(),
+                     [](const AscendTemplate& a, const AscendTemplate& b) { return a.Memory < b.Memory; });
+  }
+  std::string CommonWord() const override { return cfg_.CommonWord; }
+  FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
+                const NodeInfo* nodeInfo, const std::string& def) const override {
+    FitGates g{Vendor::ASCEND, cfg_.CommonWord, "", "",
+               "hami.io/use-" + cfg_.CommonWord + "-uuid", "hami.io/no-use-" + cfg_.CommonWord + "-uuid", hamiVnpuCore_};
+    return fitTemplate(g, devices, request, pod, nodeInfo, def);
+  }
+  // ascend/device.go:388-424
+  float ScoreNode(const PodSingleDevice& podDevices, const std::string&) const override {
+    if (!HasPrefix(cfg_.CommonWord, "Ascend910")) return 0;
+    float score = 0;
+    for (auto& containerDevices : podDevices) {
+      if (containerDevices.empty()) continue;
+      std::map<int, int> cntMap;
+      for (auto& d : containerDevices) {
+        if (!d.HasNetworkID) return 0;
+        cntMap[d.NetworkID]++;
+      }
+      int maxCnt = 0, totalCnt = 0;
+      for (auto& kv : cntMap) { if (kv.second > maxCnt) maxCnt = kv.second; totalCnt += kv.second; }
+      if (totalCnt == 0) continue;
+      score = score + (float)maxCnt / (float)totalCnt;
+    }
+    return score * (float)10;
+  }
+  // trimMemory, ascend/device.go:69-79
+  std::string trimName(int64_t m) const {
+    for (auto& t : cfg_.Templates) if (m <= t.Memory) return t.Name;
+    return "";
+  }
+  void PatchAnnotations(const Pod& pod, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
+    // ascend/device.go:221-253
+    auto it = pd.find(cfg_.CommonWord);
+    if (it != pd.end() && !it->second.empty()) {
+      std::string s = EncodePodSingleDevice(it->second);
+      annos["hami.io/" + cfg_.CommonWord + "-devices-to-allocate"] = s;
+      annos["hami.io/" + cfg_.CommonWord + "-devices-allocated"] = s;
+      annos["predicate-time"] = "";  // canonical rule 6
+      std::string vnpuMode;
+      if (auto v = anno(pod, "huawei.com/vnpu-mode")) vnpuMode = *v;
+      std::string json;
+      bool any = false;
+      for (auto& dp : it->second) {
+        for (auto& val : dp) {
+          std::string e = "{";
+          bool first = true;
+          auto add = [&](const std::string& f) { if (!first) e += ","; e += f; first = false; };
+          if (!val.UUID.empty()) add("\"UUID\":\"" + val.UUID + "\"");
+          if (vnpuMode != "hami-core") {
+            std::string temp = trimName((int64_t)val.Usedmem);
+            if (!temp.empty()) add("\"temp\":\"" + temp + "\"");
+          }
+          if (val.Usedmem != 0) add("\"memory\":" + std::to_string((int64_t)val.Usedmem));
+          if (val.Usedcores != 0) add("\"core\":" + std::to_string(val.Usedcores));
+          e += "}";
+          json += (any ? "," : "") + e;
+          any = true;
+        }
+      }
+      annos["huawei.com/" + cfg_.CommonWord] = any ? "[" + json + "]" : "null";
+    }
+  }
+
+ private:
+  AscendConfig cfg_;
+  bool hamiVnpuCore_;
+};
+
+// getNodeResources, score.go:43-52
+std::vector<DeviceUsage*> getNodeResources(NodeUsage& list, const std::string& t) {
+  std::vector<DeviceUsage*> l;
+  std::string targetType = ToLower(t);
+  for (auto& val : list.Devices.DeviceLists)
+    if (Contains(ToLower(val.Device.Type), targetType)) l.push_back(&val.Device);
+  return l;
+}
+
+// isMIGRequest, score.go:54-69
+bool isMIGRequest(const ContainerDeviceRequest& request, const std::vector<DeviceUsage*>& devices, const Pod& pod) {
+  if (request.Type != "NVIDIA") return false;
+  if (auto mode = anno(pod, "nvidia.com/vgpu-mode")) {
+    if (!Contains(*mode, "mig")) return false;
+  }
+  for (auto d : devices) if (d->Mode == "mig") return true;
+  return false;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// Scheduler
+// ---------------------------------------------------------------------------
+Scheduler::Scheduler(const Config& cfg) : cfg_(cfg) {
+  vendors_["NVIDIA"] = std::make_unique<NvidiaGPUDevices>();
+  vendors_["DCU"] = std::make_unique<DCUDevices>();
+  vendors_["MLU"] = std::make_unique<CambriconDevices>();
+  for (auto& a : cfg.Ascend) vendors_[a.CommonWord] = std::make_unique<AscendDevices>(a, cfg.AscendHamiVnpuCore);
+}
+Scheduler::~Scheduler() = default;
+
+const Devices* Scheduler::Vendor(const std::string& key) const {
+  auto it = vendors_.find(key);
+  return it == vendors_.end() ? nullptr : it->second.get();
+}
+
+void Scheduler::AddNode(const NodeInfo& info) {
+  auto it = nodeIndex_.find(info.ID);
+  std::vector<DeviceUsage> usage;
+  for (auto& kv : info.Devices) {
+    for (auto& d : kv.second) {
+      DeviceUsage u;  // buildNodeUsage, scheduler.go:665-687
+      u.ID = d.ID; u.Index = d.Index; u.Count = d.Count; u.Totalmem = d.Devmem; u.Totalcore = d.Devcore;
+      u.Mode = d.Mode; u.Type = d.Type; u.Numa = d.Numa; u.Health = d.Health;
+      u.HasNetworkID = d.HasNetworkID; u.NetworkID = d.NetworkID;
+      usage.push_back(u);
+    }
+  }
+  if (usage.size() > 12) throw std::runtime_error("oracle: >12 devices per node (canonical rule 5)");
+  if (it == nodeIndex_.end()) {
+    auto ne = std::make_unique<NodeEntry>();
+    ne->info = info;
+    ne->usage = usage;
+    nodeIndex_[info.ID] = (int)nodes_.size();
+    nodes_.push_back(std::move(ne));
+  } else {
+    NodeEntry& ne = *nodes_[it->second];
+    for (auto& u : usage)
+      for (auto& old : ne.usage)
+        if (old.ID == u.ID) { u.Used = old.Used; u.Usedmem = old.Usedmem; u.Usedcores = old.Usedcores; }
+    ne.info = info;
+    ne.usage = usage;
+    ne.alive = true;
+  }
+}
+
+bool Scheduler::RemoveNode(const std::string& name) {
+  auto it = nodeIndex_.find(name);
+  if (it == nodeIndex_.end() || !nodes_[it->second]->alive) return false;
+  nodes_[it->second]->alive = false;
+  return true;
+}
+
+// The usage a cached pod contributes: scheduler.go:773-785
+void Scheduler::applyUsage(NodeEntry& ne, const PodDevices& devs, int sign) {
+  for (auto& kv : devs)
+    for (auto& ctrdevs : kv.second)
+      for (auto& udevice : ctrdevs)
+        for (auto& d : ne.usage)
+          if (d.ID == udevice.UUID) {
+            int32_t slots = std::max(udevice.Slots, 1);
+            if (sign > 0) { d.Used = i32add(d.Used, slots); d.Usedmem = i32add(d.Usedmem, udevice.Usedmem); d.Usedcores = i32add(d.Usedcores, udevice.Usedcores); }
+            else { d.Used = i32sub(d.Used, slots); d.Usedmem = i32sub(d.Usedmem, udevice.Usedmem); d.Usedcores = i32sub(d.Usedcores, udevice.Usedcores); }
+          }
+}
+
+bool Scheduler::UsageApply(const std::string& uid, const std::string& node, const std::string& uuid,
+                           int32_t slots, int32_t mem, int32_t cores) {
+  auto it = nodeIndex_.find(node);
+  if (it == nodeIndex_.end()) return false;
+  PodInfo& pi = pods_[uid];
+  pi.NodeID = node;
+  ContainerDevice cd;
+  cd.UUID = uuid; cd.Usedmem = mem; cd.Usedcores = cores; cd.Slots = slots;
+  PodDevices one;
+  one["_"] = PodSingleDevice{ContainerDevices{cd}};
+  if (pi.Devices["_"].empty()) pi.Devices["_"].push_back({});
+  pi.Devices["_"][0].push_back(cd);
+  applyUsage(*nodes_[it->second], one, +1);
+  return true;
+}
+
+bool Scheduler::DeletePod(const std::string& uid) {
+  auto it = pods_.find(uid);
+  if (it == pods_.end()) return false;
+  auto n = nodeIndex_.find(it->second.NodeID);
+  if (n != nodeIndex_.end()) applyUsage(*nodes_[n->second], it->second.Devices, -1);
+  pods_.erase(it);
+  return true;
+}
+
+// buildNodeUsage (scheduler.go:654-690) + the usage half of getNodesUsage (:757-842)
+NodeUsage Scheduler::BuildNodeUsage(const NodeInfo& info, const Pod& pod) const {
+  NodeUsage nu;
+  nu.Info = &info;
+  nu.Devices.Policy = GetGPUSchedulerPolicyByPod(cfg_.GPUSchedulerPolicy, pod);
+  bool nb = false;  // numaBindingRequested, scheduler.go:641-652
+  if (auto v = anno(pod, "nvidia.com/numa-bind")) { bool b; if (ParseBool(*v, b) && b) nb = true; }
+  nu.Devices.NumaBind = nb;
+  auto it = nodeIndex_.find(info.ID);
+  const NodeEntry& ne = *nodes_[it->second];
+  const std::vector<DeviceUsage>& src = faithful && (size_t)it->second < rebuilt_.size() ? rebuilt_[it->second] : ne.usage;
+  for (auto& u : src) {
+    DeviceListsScore ds;
+    ds.Device = u;
+    nu.Devices.DeviceLists.push_back(ds);
+  }
+  return nu;
+}
+
+std::vector<DeviceUsage> Scheduler::Snapshot(const std::string& node) const {
+  auto it = nodeIndex_.find(node);
+  if (it == nodeIndex_.end()) return {};
+  return nodes_[it->second]->usage;
+}
+
+// fitInDevices, score.go:81-137
+bool Scheduler::FitInDevices(NodeUsage& node, const ContainerDeviceRequests& requests, const Pod& pod,
+                             PodDevices& devinput, const DeviceScoringWeights& weights, std::string& reason) const {
+  for (auto& dl : node.Devices.DeviceLists) dl.ComputeScore(requests, weights);
+  for (auto& kv : requests) {  // canonical rule 4: sorted key order
+    const ContainerDeviceRequest& k = kv.second;
+    node.Devices.Sort();
+    const Devices* devPlugin = Vendor(k.Type);
+    if (!devPlugin) { reason = "Device type not found"; return false; }
+    std::vector<DeviceUsage*> typeDevices = getNodeResources(node, k.Type);
+    if ((int)k.Nums > (int)typeDevices.size() && !isMIGRequest(k, typeDevices, pod)) {
+      reason = "NodeInsufficientDevice";
+      return false;
+    }
+    FitResult fr = devPlugin->Fit(typeDevices, k, pod, node.Info, cfg_.GPUSchedulerPolicy);
+    if (!fr.fit) { reason = fr.reason; return false; }
+    for (auto& val : fr.devs) {
+      DeviceUsage* d = nullptr;
+      for (auto& v : node.Devices.DeviceLists) if (v.Device.ID == val.UUID) { d = &v.Device; break; }
+      if (!d) { reason = "Device with UUID \"" + val.UUID + "\" not found on node " + (node.Info ? node.Info->ID : "") + " after Fit"; return false; }
+      devPlugin->AddResourceUsage(*d, val);
+    }
+    devinput[k.Type].push_back(fr.devs);
+  }
+  return true;
+}
+
+// scoreNode, score.go:294-346 (+ allocateInitContainers :226-254, allocateAppContainers :256-286,
+// snapshot/update/applyPeakUsage :154-224; the peak map only feeds the discarded original node)
+NodeScoreResult Scheduler::ScoreNode(const std::string& nodeID, NodeUsage& node, const Pod& pod,
+                                     const std::string& userNodePolicy, const DeviceScoringWeights& weights) const {
+  NodeScoreResult res;
+  std::set<std::string> baseTypes;  // nodeDeviceBaseTypes, score.go:71-79
+  for (auto& dl : node.Devices.DeviceLists) baseTypes.insert(dl.Device.Type);
+  int numInit = pod.NumInitContainers;
+
+  PodDevices initAllocs;
+  bool haveInit = false;
+  if (numInit > 0) {
+    haveInit = true;
+    for (int i = 0; i < (int)pod.Reqs.size(); i++) {
+      if (i >= numInit) break;
+      const ContainerDeviceRequests& req = pod.Reqs[i];
+      if (req.empty()) {
+        for (auto& typ : baseTypes) initAllocs[typ].push_back({});
+        continue;
+      }
+      NodeUsage nodeCopy = node;
+      std::string reason;
+      if (!FitInDevices(nodeCopy, req, pod, initAllocs, weights, reason)) { res.fit = false; res.reason = reason; return res; }
+      for (auto& typ : baseTypes)
+        if ((int)initAllocs[typ].size() == i) initAllocs[typ].push_back({});
+    }
+  }
+
+  NodeUsage appNodeCopy = node;
+  NodeScore score;
+  score.NodeID = nodeID;
+  score.Score = ComputeDefaultScore(appNodeCopy.Devices);
+
+  int appIndex = 0;
+  for (int ctrid = 0; ctrid < (int)pod.Reqs.size(); ctrid++) {
+    if (ctrid < numInit) continue;
+    const ContainerDeviceRequests& n = pod.Reqs[ctrid];
+    int sums = 0;
+    for (auto& kv : n) sums += (int)kv.second.Nums;
+    if (sums == 0) {
+      for (auto& typ : baseTypes) score.Devices[typ].push_back({});
+      appIndex++;
+      continue;
+    }
+    std::string reason;
+    if (!FitInDevices(appNodeCopy, n, pod, score.Devices, weights, reason)) { res.fit = false; res.reason = reason; return res; }
+    for (auto& typ : baseTypes)
+      if ((int)score.Devices[typ].size() == appIndex) score.Devices[typ].push_back({});
+    appIndex++;
+  }
+
+  if (numInit > 0 && haveInit) {
+    for (auto& kv : initAllocs) {
+      PodSingleDevice merged = kv.second;
+      auto& cur = score.Devices[kv.first];
+      merged.insert(merged.end(), cur.begin(), cur.end());
+      cur = merged;
+    }
+  }
+
+  // OverrideScore, policy/node_policy.go:67-95 (sorted key order)
+  float devScore = 0;
+  for (auto& kv : score.Devices) {
+    const Devices* dev = Vendor(kv.first);
+    if (!dev) continue;
+    devScore = devScore + dev->ScoreNode(kv.second, userNodePolicy);
+  }
+  score.Score = score.Score + devScore;
+  res.fit = true;
+  res.score = score;
+  return res;
+}
+
+void Scheduler::scoreRange(const std::vector<int>& cand, size_t lo, size_t hi, const Pod& pod,
+                           const std::string& userNodePolicy, const DeviceScoringWeights& w,
+                           std::vector<NodeScoreResult>& out) const {
+  for (size_t i = lo; i < hi; i++) {
+    if (cand[i] < 0) continue;
+    const NodeEntry& ne = *nodes_[cand[i]];
+    NodeUsage nu = BuildNodeUsage(ne.info, pod);
+    out[i] = ScoreNode(ne.info.ID, nu, pod, userNodePolicy, w);
+  }
+}
+
+// Scheduler.Filter, scheduler.go:1067-1154
+FilterResult Scheduler::Filter(const Pod& pod, const std::vector<std::string>* nodeNames) {
+  FilterResult fr;
+  bool hasHAMiResource = false;
+  for (auto& reqMap : pod.Reqs) if (!reqMap.empty()) { hasHAMiResource = true; break; }
+  if (!hasHAMiResource) { fr.status = 2; return fr; }
+
+  // TakeAndDeletePod, scheduler.go:1092-1094
+  DeletePod(pod.UID);
+
+  std::vector<int> cand;
+  std::vector<std::string> names;
+  if (nodeNames) {
+    for (auto& n : *nodeNames) {
+      auto it = nodeIndex_.find(n);
+      names.push_back(n);
+      cand.push_back(it == nodeIndex_.end() || !nodes_[it->second]->alive ? -1 : it->second);
+    }
+  } else {
+    for (size_t i = 0; i < nodes_.size(); i++)
+      if (nodes_[i]->alive) { cand.push_back((int)i); names.push_back(nodes_[i]->info.ID); }
+  }
+
+  // calcScoreWithOptions, score.go:360-419
+  DeviceScoringWeights weights;
+  if (auto v = anno(pod, "hami.io/device-scoring-weights")) {
+    std::string err;
+    if (!ParseDeviceScoringWeights(*v, weights, err)) { fr.status = -4; fr.error = err; return fr; }
+  }
+  std::string userNodePolicy = cfg_.NodeSchedulerPolicy;  // resolveNodeSchedulerPolicy, score.go:139-146
+  if (auto v = anno(pod, "hami.io/node-scheduler-policy")) userNodePolicy = *v;
+
+  if (faithful) {
+    // getNodesUsage, scheduler.go:744-842: fresh usage for EVERY registered node, then replay every cached pod
+    rebuilt_.assign(nodes_.size(), {});
+    for (size_t i = 0; i < nodes_.size(); i++) {
+      rebuilt_[i] = nodes_[i]->usage;  // deep copy per node (nodes.go:150-170)
+      for (auto& d : rebuilt_[i]) { d.Used = 0; d.Usedmem = 0; d.Usedcores = 0; }
+    }
+    for (auto& kv : pods_) {
+      auto n = nodeIndex_.find(kv.second.NodeID);
+      if (n == nodeIndex_.end()) continue;
+      for (auto& pd : kv.second.Devices)
+        for (auto& ctrdevs : pd.second)
+          for (auto& udevice : ctrdevs)
+            for (auto& d : rebuilt_[n->second])
+              if (d.ID == udevice.UUID) {
+                int32_t slots = std::max(udevice.Slots, 1);
+                d.Used = i32add(d.Used, slots);
+                d.Usedmem = i32add(d.Usedmem, udevice.Usedmem);
+                d.Usedcores = i32add(d.Usedcores, udevice.Usedcores);
+              }
+    }
+  }
+  std::vector<NodeScoreResult> results(cand.size());
+  int T = std::max(1, std::min(threads, (int)cand.size()));
+  if (T == 1) {
+    scoreRange(cand, 0, cand.size(), pod, userNodePolicy, weights, results);
+  } else {
+    std::vector<std::thread> th;
+    size_t chunk = (cand.size() + T - 1) / T;
+    for (int t = 0; t < T; t++) {
+      size_t lo = t * chunk, hi = std::min(cand.size(), lo + chunk);
+      if (lo >= hi) break;
+      th.emplace_back([&, lo, hi] { scoreRange(cand, lo, hi, pod, userNodePolicy, weights, results); });
+    }
+    for (auto& t : th) t.join();
+  }
+
+  // sort.Sort(nodeScores) + take last (scheduler.go:1117-1118) under canonical rules 2-3
+  int best = -1;
+  bool spread = userNodePolicy == "spread";
+  for (size_t i = 0; i < cand.size(); i++) {
+    if (cand[i] < 0) { fr.failedNodes.push_back({names[i], "node unregistered"}); continue; }
+    if (!results[i].fit) { fr.failedNodes.push_back({names[i], results[i].reason}); continue; }
+    if (best < 0) { best = (int)i; continue; }
+    float s = results[i].score.Score, b = results[best].score.Score;
+    if (spread ? (s <= b) : (s >= b)) best = (int)i;
+  }
+  if (best < 0) { fr.status = 1; return fr; }
+
+  fr.status = 0;
+  fr.nodeIndex = best;
+  fr.chosen = results[best].score;
+  const NodeScore& m = fr.chosen;
+  fr.annotations["hami.io/vgpu-node"] = m.NodeID;
+  fr.annotations["hami.io/vgpu-time"] = "";  // canonical rule 6
+  for (auto& kv : vendors_) kv.second->PatchAnnotations(pod, fr.annotations, m.Devices);
+
+  // commit: scheduler.go:1132-1138
+  PodDevices effective = CollapseInitContainerUsage(pod.NumInitContainers, m.Devices);
+  PodInfo pi;
+  pi.NodeID = m.NodeID;
+  pi.Devices = effective;
+  applyUsage(*nodes_[cand[best]], effective, +1);
+  pods_[pod.UID] = pi;
+  return fr;
+}
+
+}  // namespace oracle

@@ -1,0 +1,266 @@
+/*
+ * oracle.h — TEST INFRASTRUCTURE ONLY.
+ *
+ * CPU restatement (C++17, strings and maps, no CUDA) of the HAMi scheduler's
+ * Filter/Score hot path, following the reference Go sources line by line
+ * (each function cites the reference file:line it restates; paths relative to
+ * the reference tree root, Project-HAMi/HAMi v2.10.0).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may link, load or execute this code, and only as the
+ * checker or the timed CPU baseline.  The product (k8s-vgpu-scheduler_b200/)
+ * never calls into it: it has no CPU fallback.
+ *
+ * PARITY STATUS: pinned.  tests/test_oracle_golden.py replays the reference's
+ * own known-answer tests (the JSON fixtures under tests/golden, extracted from
+ * the reference's _test.go files by tools/extract_golden.py) against this code.  The Go
+ * reference itself cannot be built here (no Go toolchain, no module cache).
+ *
+ * CANONICAL LINEARISATION — the reference is nondeterministic
+ * in the places below (Go map iteration, goroutine completion order, unstable
+ * sort); this oracle AND the CUDA engine both fix them the same way:
+ *  1. Nodes are evaluated in NodeNames order; a node's index is its position
+ *     in the candidate list.
+ *  2. The winner has the best score: max, or min when the node policy is
+ *     exactly "spread" (policy/node_policy.go:48-54).
+ *  3. Among equal scores the HIGHEST candidate index wins (what sort.Sort +
+ *     take-last gives for a stable sort of nodes arriving in order).
+ *  4. One container's request types are processed in sorted map-key order
+ *     (score.go:88 ranges over a Go map).
+ *  5. A node's devices start in registration order, vendors in sorted vendor
+ *     key order (scheduler.go:665-687 ranges over a map); <=12 devices per
+ *     node is asserted so Go's sort.Sort is the stable insertion sort.
+ *  6. hami.io/vgpu-time and predicate-time carry "" instead of a timestamp.
+ *  7. Ascend NetworkID groups with equal candidate counts are taken in
+ *     ascending NetworkID (ascend/device.go:653-663); Ascend910C cards with
+ *     equal size in ascending card id idx/2 (ascend/device.go:689-702).
+ *  Additionally OverrideScore sums vendor ScoreNode results in sorted type-key
+ *  order (policy/node_policy.go:69 ranges over a map).
+ *
+ * Not restated (outside the built scope, the oracle refuses such inputs):
+ * dynamic MIG placement (nvidia/device.go:602-639, mig_topology.go) and
+ * namespace ResourceQuota (device/quota.go) — every BASELINE config runs
+ * without either; FitQuota returns true when the namespace has no quota entry
+ * (quota.go:73-76).
+ */
+#ifndef HAMI_ORACLE_H_
+#define HAMI_ORACLE_H_
+
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <optional>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+namespace oracle {
+
+// ---- pkg/device/devices.go:106-236 ------------------------------------------
+struct DeviceUsage {               // devices.go:106-125
+  std::string ID;
+  unsigned Index = 0;
+  int32_t Used = 0, Count = 0, Usedmem = 0, Totalmem = 0, Totalcore = 0, Usedcores = 0;
+  std::string Mode;
+  int Numa = 0;
+  std::string Type;
+  bool Health = true;
+  bool HasNetworkID = false;       // CustomInfo["NetworkID"] present
+  int NetworkID = 0;
+};
+
+struct DeviceInfo {                // devices.go:127-144
+  std::string ID;
+  unsigned Index = 0;
+  int32_t Count = 0, Devmem = 0, Devcore = 0;
+  std::string Type;
+  int Numa = 0;
+  std::string Mode;
+  bool Health = true;
+  std::string DeviceVendor;
+  bool HasNetworkID = false;
+  int NetworkID = 0;
+  std::map<std::string, int> PairScores;  // DevicePairScore.Scores
+};
+
+struct NodeInfo {                  // devices.go:170-174 (+ the node annotations Fit reads)
+  std::string ID;
+  std::map<std::string, std::vector<DeviceInfo>> Devices;  // sorted vendor key = canonical rule 5
+  std::optional<std::string> DeviceCordon;                  // hami.io/device-cordon
+  std::optional<std::string> HamiVnpuCore;                  // hami-vnpu-core
+};
+
+struct ContainerDevice {           // devices.go:205-216
+  int Idx = 0;
+  std::string UUID, Type;
+  int32_t Usedmem = 0, Usedcores = 0, Slots = 0;
+  bool HasNetworkID = false;       // CustomInfo carried by the Ascend Fit (ascend/device.go:573)
+  int NetworkID = 0;
+};
+
+struct ContainerDeviceRequest {    // devices.go:222-228
+  int32_t Nums = 0;
+  std::string Type;
+  int32_t Memreq = 0, MemPercentagereq = 0, Coresreq = 0;
+};
+
+using ContainerDevices = std::vector<ContainerDevice>;
+using ContainerDeviceRequests = std::map<std::string, ContainerDeviceRequest>;  // sorted key = canonical rule 4
+using PodSingleDevice = std::vector<ContainerDevices>;
+using PodDeviceRequests = std::vector<ContainerDeviceRequests>;
+using PodDevices = std::map<std::string, PodSingleDevice>;
+
+struct Pod {                       // the parts of corev1.Pod the path reads
+  std::string UID, Namespace, Name;
+  std::map<std::string, std::string> Annotations;
+  int NumInitContainers = 0;
+  PodDeviceRequests Reqs;          // device.Resourcereqs(pod), devices.go:639-691
+};
+
+struct DeviceScoringWeights { int64_t Slot = 1, Core = 1, Memory = 1; };  // util/device_scoring_weights.go:29-38
+
+// ---- pkg/scheduler/policy ---------------------------------------------------
+struct DeviceListsScore {          // policy/gpu_policy.go:28-32
+  DeviceUsage Device;
+  float Score = 0;
+  void ComputeScore(const ContainerDeviceRequests& requests, const DeviceScoringWeights& w);
+};
+
+struct DeviceUsageList {           // policy/gpu_policy.go:34-40
+  std::vector<DeviceListsScore> DeviceLists;
+  std::string Policy;
+  bool NumaBind = false;
+  bool Less(int i, int j) const;
+  void Sort();                     // Go sort.Sort for n <= 12: stable insertion sort
+};
+
+struct NodeUsage {                 // pkg/scheduler/nodes.go:30-34
+  const NodeInfo* Info = nullptr;
+  DeviceUsageList Devices;
+};
+
+struct NodeScore {                 // policy/node_policy.go:27-33
+  std::string NodeID;
+  PodDevices Devices;
+  float Score = 0;
+};
+
+// ---- vendor seam: pkg/device/devices.go:34-48 --------------------------------
+struct FitResult {
+  bool fit = false;
+  ContainerDevices devs;           // tmpDevs[k.Type]
+  std::string reason;
+};
+
+class Devices {
+ public:
+  virtual ~Devices() = default;
+  virtual std::string CommonWord() const = 0;
+  virtual FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request,
+                        const Pod& pod, const NodeInfo* nodeInfo, const std::string& gpuPolicyDefault) const = 0;
+  virtual float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy) const { return 0; }
+  virtual void AddResourceUsage(DeviceUsage& n, const ContainerDevice& ctr) const;
+  virtual void PatchAnnotations(const Pod& pod, std::map<std::string, std::string>& annos, const PodDevices& pd) const = 0;
+};
+
+struct AscendTemplate { std::string Name; int64_t Memory = 0; };
+struct AscendConfig {
+  std::string CommonWord;
+  int64_t MemoryAllocatable = 0, MemoryCapacity = 0;
+  std::vector<AscendTemplate> Templates;
+};
+
+struct Config {
+  std::string NodeSchedulerPolicy = "binpack";   // cmd/scheduler/main.go:70
+  std::string GPUSchedulerPolicy = "spread";     // cmd/scheduler/main.go:71
+  std::vector<AscendConfig> Ascend;
+  bool AscendHamiVnpuCore = false;
+};
+
+struct PodInfo {                   // pkg/device/pods.go:33-40
+  std::string NodeID;
+  PodDevices Devices;              // collapsed
+};
+
+struct FilterResult {
+  int status = 0;                  // HS_FIT / HS_NOFIT / HS_PASSTHROUGH / <0
+  std::string error;
+  int nodeIndex = -1;
+  NodeScore chosen;
+  std::map<std::string, std::string> annotations;
+  std::vector<std::pair<std::string, std::string>> failedNodes;  // candidate order
+};
+
+struct NodeScoreResult {           // score.go:288-292
+  bool fit = false;
+  NodeScore score;
+  std::string reason;
+};
+
+class Scheduler {
+ public:
+  explicit Scheduler(const Config& cfg);
+  ~Scheduler();
+
+  // nodeManager.addNode / rmNodeDevices (nodes.go:76-148)
+  void AddNode(const NodeInfo& info);
+  bool RemoveNode(const std::string& name);
+  // podManager.AddPod fed by the informer (pods.go:57-97)
+  bool UsageApply(const std::string& uid, const std::string& node, const std::string& uuid,
+                  int32_t slots, int32_t mem, int32_t cores);
+  bool DeletePod(const std::string& uid);
+
+  // Scheduler.Filter (scheduler.go:1067-1154). nodeNames == nullptr: all nodes in registration order.
+  FilterResult Filter(const Pod& pod, const std::vector<std::string>* nodeNames);
+
+  // scoreNode (score.go:294-346) on an explicit usage (what Test_calcScore drives).
+  NodeScoreResult ScoreNode(const std::string& nodeID, NodeUsage& node, const Pod& pod,
+                            const std::string& userNodePolicy, const DeviceScoringWeights& w) const;
+  // fitInDevices (score.go:81-137)
+  bool FitInDevices(NodeUsage& node, const ContainerDeviceRequests& requests, const Pod& pod,
+                    PodDevices& devinput, const DeviceScoringWeights& w, std::string& reason) const;
+
+  // buildNodeUsage + usage of every cached pod (scheduler.go:654-690,744-863)
+  NodeUsage BuildNodeUsage(const NodeInfo& info, const Pod& pod) const;
+  std::vector<DeviceUsage> Snapshot(const std::string& node) const;
+
+  const Devices* Vendor(const std::string& key) const;
+  const Config& config() const { return cfg_; }
+
+  bool faithful = false;   // true: rebuild usage from the whole pod cache on every Filter (scheduler.go:744-863)
+  int threads = 1;         // node fan-out (the reference runs one goroutine per node, score.go:378-406)
+  size_t NodeCount() const { return nodes_.size(); }
+
+ private:
+  struct NodeEntry {
+    NodeInfo info;
+    std::vector<DeviceUsage> usage;  // lean mode: incremental usage, registration order
+    bool alive = true;
+  };
+  void applyUsage(NodeEntry& ne, const PodDevices& devs, int sign);
+  void scoreRange(const std::vector<int>& cand, size_t lo, size_t hi, const Pod& pod,
+                  const std::string& userNodePolicy, const DeviceScoringWeights& w,
+                  std::vector<NodeScoreResult>& out) const;
+  Config cfg_;
+  std::map<std::string, std::unique_ptr<Devices>> vendors_;
+  std::vector<std::unique_ptr<NodeEntry>> nodes_;            // registration order (slot)
+  std::unordered_map<std::string, int> nodeIndex_;
+  std::unordered_map<std::string, PodInfo> pods_;           // podManager
+  std::vector<std::vector<DeviceUsage>> rebuilt_;           // faithful mode: per-Filter usage rebuild
+};
+
+// ---- free functions restated from the reference (also exported for the golden tests) ----
+std::string GenReason(const std::map<std::string, int>& reasons, int cards);          // common/common.go:46-53
+bool CheckUUID(const std::map<std::string, std::string>& annos, const std::string& id,
+               const std::string& useKey, const std::string& noUseKey);                  // devices.go:693-713
+bool CheckType(const std::map<std::string, std::string>& annos, const std::string& cardType,
+               const std::string& useKey, const std::string& noUseKey);                  // devices.go:719-738
+bool PolicyContains(const std::string& policy, const std::string& name);                 // util/util.go:290-298
+std::string GetGPUSchedulerPolicyByPod(const std::string& def, const Pod& pod);         // util/util.go:277-285
+bool ParseDeviceScoringWeights(const std::string& v, DeviceScoringWeights& out, std::string& err);  // util/device_scoring_weights.go:43-102
+PodDevices CollapseInitContainerUsage(int numInit, const PodDevices& raw);               // device/initContainer.go:36-114
+std::string EncodePodSingleDevice(const PodSingleDevice& pd);                            // devices.go:451-484
+float ComputeDefaultScore(const DeviceUsageList& devices);                               // policy/node_policy.go:106-130
+
+}  // namespace oracle
+#endif

@@ -1,0 +1,76 @@
+/*
+ * oracle_capi.h — TEST INFRASTRUCTURE ONLY.  C entry points of the CPU oracle
+ * (oracle.h) so tests/ and bench.py can drive it with ctypes.  It reuses the
+ * plain input/output structs of include/hami_sched.h so the very same buffers
+ * can be handed to the oracle and to the CUDA engine.
+ */
+#ifndef HAMI_ORACLE_CAPI_H_
+#define HAMI_ORACLE_CAPI_H_
+#include <stddef.h>
+#include <stdint.h>
+#include "../include/hami_sched.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct oracle_handle oracle_handle;
+
+/* device.DeviceUsage literal (devices.go:106-125) + DeviceListsScore.Score */
+typedef struct oracle_dev {
+  const char* id;
+  uint32_t    index;
+  int32_t     used, count, usedmem, totalmem, totalcore, usedcores;
+  const char* mode;
+  int32_t     numa;
+  const char* type;
+  uint8_t     health;
+  int32_t     network_id; /* -1 absent */
+  float       score;
+} oracle_dev;
+
+oracle_handle* oracle_create(const hs_config* cfg);
+void    oracle_destroy(oracle_handle* o);
+/* faithful=1: rebuild usage from the whole pod cache on every Filter like scheduler.go:744-863; threads: node fan-out */
+void    oracle_set_mode(oracle_handle* o, int faithful, int threads);
+int32_t oracle_node_upsert(oracle_handle* o, const hs_node_info* node);
+int32_t oracle_node_remove(oracle_handle* o, const char* name);
+int32_t oracle_usage_apply(oracle_handle* o, const char* pod_uid, const char* node, const char* uuid,
+                           int32_t slots, int32_t usedmem, int32_t usedcores);
+int32_t oracle_pod_delete(oracle_handle* o, const char* pod_uid);
+int32_t oracle_filter(oracle_handle* o, const hs_pod* pod, const char* const* node_names, uint32_t n_names,
+                      hs_filter_result* out);
+int32_t oracle_snapshot_node(oracle_handle* o, const char* node, hs_device_usage_row* rows, uint32_t cap);
+const char* oracle_last_error(const oracle_handle* o);
+
+/* scoreNode (score.go:294-346) on an explicit NodeUsage, as Test_calcScore drives it.
+ * list_policy NULL / numa_bind <0: derive from the pod like buildNodeUsage. status HS_FIT or HS_NOFIT (failed[0].reason). */
+int32_t oracle_score_node(oracle_handle* o, const char* node_id, const oracle_dev* devs, uint32_t n,
+                          const char* list_policy, int32_t numa_bind, const hs_pod* pod,
+                          const hs_node_info* node_info, hs_filter_result* out);
+/* fitInDevices (score.go:81-137) for ONE container's request map. Returns 1 fit / 0 no fit (reason in out->failed[0]). */
+int32_t oracle_fit_in_devices(oracle_handle* o, const oracle_dev* devs, uint32_t n, const char* list_policy,
+                              int32_t numa_bind, const hs_container* ctr, const hs_pod* pod,
+                              const hs_node_info* node_info, hs_filter_result* out);
+/* <vendor>.Fit on an explicit, already ordered device list. Returns 1/0; entries = tmpDevs[k.Type]. */
+int32_t oracle_fit(oracle_handle* o, const char* vendor_key, const oracle_dev* devs, uint32_t n,
+                   const hs_container_request* req, const hs_pod* pod, const hs_node_info* node_info,
+                   hs_filter_result* out);
+
+float   oracle_compute_score(const oracle_dev* d, const hs_container_request* reqs, uint32_t n,
+                             int64_t w_slot, int64_t w_core, int64_t w_mem);
+int32_t oracle_less(const char* policy, int32_t numa_bind, const oracle_dev* a, const oracle_dev* b);
+void    oracle_sort(const char* policy, int32_t numa_bind, const oracle_dev* devs, uint32_t n, int32_t* order_out);
+float   oracle_node_default_score(const oracle_dev* devs, uint32_t n);
+int32_t oracle_check_uuid(const hs_kv* annos, uint32_t n, const char* id, const char* use_key, const char* nouse_key);
+int32_t oracle_check_type(const hs_kv* annos, uint32_t n, const char* card_type, const char* use_key, const char* nouse_key);
+int32_t oracle_parse_weights(const char* value, int64_t out3[3]);
+/* reasons: HS_R_COUNT counts indexed by the HS_R_* enum */
+int32_t oracle_gen_reason(const int32_t* counts, int32_t cards, char* buf, size_t cap);
+/* CollapseInitContainerUsage (initContainer.go:36-114): entries in, collapsed entries out (idx field = Slots). */
+int32_t oracle_collapse(const hs_alloc_entry* in, uint32_t n_in, uint32_t n_init, hs_alloc_entry* out, uint32_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
