@@ -1,0 +1,1245 @@
+// hs_engine.cu — host side of the B200 Filter/Score engine and its C ABI
+// (include/hami_sched.h).  It is the C++ mirror of the pieces of pkg/scheduler the
+// hot path touches: nodeManager (inventory), podManager (what each pod holds),
+// the request/annotation plumbing around Filter, and the result encoding.  Strings
+// (types, UUIDs, policies, annotations) are resolved to integers HERE; the kernels in
+// hs_kernels.cu only see the SoA inventory and integer request descriptors.
+// There is no CPU fallback: without a CUDA device hs_create fails.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <array>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <set>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/hami_sched.h"
+#include "hs_types.cuh"
+
+extern "C" int hs_launch_decide(const KernelArgs* ka, int grid, int block, cudaStream_t stream);
+extern "C" int hs_decide_max_blocks(int block, int device);
+extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int grid, int block, cudaStream_t stream);
+extern "C" int hs_launch_commit(const KernelArgs* ka, int op, unsigned long long win, cudaStream_t stream);
+
+namespace {
+
+std::string g_create_error;
+
+// ---- Go string helpers (ASCII subset, as the reference's inputs are) ------------------------
+bool isSpace(unsigned char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\v' || c == '\f' || c == '\r'; }
+std::string trimSpace(const std::string& s) {
+  size_t a = 0, b = s.size();
+  while (a < b && isSpace((unsigned char)s[a])) a++;
+  while (b > a && isSpace((unsigned char)s[b - 1])) b--;
+  return s.substr(a, b - a);
+}
+std::vector<std::string> splitComma(const std::string& s) {
+  std::vector<std::string> out;
+  size_t start = 0;
+  for (;;) {
+    size_t p = s.find(',', start);
+    if (p == std::string::npos) { out.push_back(s.substr(start)); break; }
+    out.push_back(s.substr(start, p - start));
+    start = p + 1;
+  }
+  return out;
+}
+std::string upper(std::string s) { for (auto& c : s) if (c >= 'a' && c <= 'z') c = (char)(c - 32); return s; }
+std::string lower(std::string s) { for (auto& c : s) if (c >= 'A' && c <= 'Z') c = (char)(c + 32); return s; }
+bool parseBoolTrue(const std::string& s) {  // strconv.ParseBool(s) == (true, nil)
+  return s == "1" || s == "t" || s == "T" || s == "TRUE" || s == "true" || s == "True";
+}
+bool policyContains(const std::string& policy, const char* name) {  // util/util.go:290-298
+  for (auto& p : splitComma(policy)) if (trimSpace(p) == name) return true;
+  return false;
+}
+
+// device.CheckType, devices.go:719-738, for one card type
+bool checkType(const std::string* use, const std::string* nouse, const std::string& cardTypeUpper) {
+  auto match = [&](const std::string& list) {
+    for (auto& t0 : splitComma(list)) {
+      std::string t = trimSpace(t0);
+      if (!t.empty() && cardTypeUpper.find(upper(t)) != std::string::npos) return true;
+    }
+    return false;
+  };
+  if (use && !trimSpace(*use).empty() && !match(*use)) return false;
+  if (nouse && !trimSpace(*nouse).empty() && match(*nouse)) return false;
+  return true;
+}
+
+// util.ParseDeviceScoringWeights, util/device_scoring_weights.go:58-102
+bool parseWeights(const std::string& value, int64_t w[3]) {
+  w[0] = w[1] = w[2] = 0;
+  auto parts = splitComma(value);
+  if (parts.size() != 3) return false;
+  std::set<std::string> seen;
+  for (auto& part : parts) {
+    std::string p = trimSpace(part);
+    size_t eq = p.find('=');
+    if (eq == std::string::npos) return false;
+    std::string key = trimSpace(p.substr(0, eq)), val = trimSpace(p.substr(eq + 1));
+    if (seen.count(key)) return false;
+    if (val.empty()) return false;
+    size_t i = 0;
+    bool neg = false;
+    if (val[0] == '+' || val[0] == '-') { neg = val[0] == '-'; i = 1; }
+    if (i >= val.size()) return false;
+    unsigned long long acc = 0;
+    for (; i < val.size(); i++) {
+      if (val[i] < '0' || val[i] > '9') return false;
+      unsigned long long d = (unsigned long long)(val[i] - '0');
+      if (acc > (0x8000000000000000ULL - d) / 10) return false;
+      acc = acc * 10 + d;
+    }
+    if (!neg && acc > 0x7fffffffffffffffULL) return false;
+    if (neg && acc != 0) return false;  // negative weight
+    int64_t v = (int64_t)acc;
+    if (key == "slot") w[0] = v; else if (key == "core") w[1] = v; else if (key == "memory") w[2] = v; else return false;
+    seen.insert(key);
+  }
+  return !(w[0] == 0 && w[1] == 0 && w[2] == 0);
+}
+
+struct DevSlot {
+  std::string uuid, type, mode, vendor;
+  uint32_t index = 0;
+  int32_t count = 0, devmem = 0, devcore = 0, numa = 0, network_id = -1;
+  bool health = true;
+  int type_id = 0, mode_id = 0, vendor_id = 0;
+};
+
+struct NodeSlot {
+  std::string name;
+  std::vector<DevSlot> devs;
+  bool alive = false;
+  bool has_cordon = false;
+  std::string cordon;
+  int vnpu = -1;
+  std::vector<std::string> base_types;  // nodeDeviceBaseTypes, score.go:71-79 (sorted, unique)
+};
+
+struct VendorInfo {
+  int id;
+  std::string word;
+  std::string use_type, nouse_type, use_uuid, nouse_uuid;
+  std::string to_allocate, allocated;   // InRequestDevices / SupportDevices annotation keys
+  bool ascend = false, ascend910 = false;
+  std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
+};
+
+struct PodRec {           // podManager entry: what to subtract when the pod goes away
+  int node;
+  int4 delta[HS_D];
+};
+
+struct EntryMeta {
+  std::string type;       // k.Type == PodDevices key
+  int container;
+  int vendor;
+};
+
+struct OpMeta {           // host-side memory of one op of the current batch
+  int kind = OP_NOP;      // OP_FILTER / OP_RELEASE / OP_NOP
+  int status = HS_OK;     // compile-time verdict: HS_PASSTHROUGH / HS_ERR_*
+  std::string uid, vnpu_mode;
+  int n_ctr = 0, n_init = 0;
+  std::vector<EntryMeta> entries;
+  std::vector<uint8_t> ctr_begin;
+  int user_op = -1;       // index of the caller's op this device op belongs to
+};
+
+template <class T>
+struct DBuf {             // device buffer + pinned host mirror
+  T* d = nullptr;
+  T* h = nullptr;
+  size_t cap = 0;
+  bool ensure(size_t n) {
+    if (n <= cap) return true;
+    size_t ncap = std::max<size_t>(n, cap * 2);
+    if (ncap < 16) ncap = 16;
+    T* nd = nullptr; T* nh = nullptr;
+    if (cudaMalloc(&nd, ncap * sizeof(T)) != cudaSuccess) return false;
+    if (cudaMallocHost(&nh, ncap * sizeof(T)) != cudaSuccess) { cudaFree(nd); return false; }
+    if (d) cudaFree(d);
+    if (h) cudaFreeHost(h);
+    d = nd; h = nh; cap = ncap;
+    return true;
+  }
+  void release() { if (d) cudaFree(d); if (h) cudaFreeHost(h); d = nullptr; h = nullptr; cap = 0; }
+};
+
+}  // namespace
+
+struct hs_handle {
+  std::string err;
+  std::string node_policy = "binpack", gpu_policy = "spread";
+  bool ascend_vnpu_default = false;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double last_ms = 0;
+  uint64_t launches = 0;
+  int block = 64;
+
+  std::vector<VendorInfo> vendors;
+  std::unordered_map<std::string, int> vendor_by_word;
+  std::vector<std::string> types, types_lower, types_upper;
+  std::unordered_map<std::string, int> type_ids;
+  std::vector<std::string> modes;
+
+  std::vector<NodeSlot> nodes;
+  std::unordered_map<std::string, int> node_by_name;
+  std::unordered_map<std::string, std::vector<uint32_t>> uuid_index;  // uuid -> (slot<<8 | dev)
+  int n_alive = 0;
+  bool has_dead = false;
+
+  // inventory mirrors (host) + device arrays
+  std::vector<int4> h_dyn, h_stat;
+  std::vector<uint32_t> h_flags;
+  std::vector<int16_t> h_pair;
+  int4* d_dyn = nullptr; int4* d_stat = nullptr; uint32_t* d_flags = nullptr; int16_t* d_pair = nullptr;
+  int cap_nodes = 0;       // slots allocated (multiple of HS_TILE)
+  int dirty_lo = 1 << 30, dirty_hi = -1;   // tile range to upload before the next launch
+
+  std::unordered_map<std::string, PodRec> pods;
+
+  // batch staging
+  DBuf<DevPod> b_pods;
+  DBuf<DevEntry> b_entries;
+  DBuf<uint32_t> b_uuid;
+  DBuf<int4> b_rel;
+  DBuf<DevDecision> b_dec;
+  DBuf<DevAlloc> b_alloc;
+  DBuf<int4> b_delta;
+  DBuf<unsigned long long> b_best;
+  DBuf<DevFail> b_fail;
+  DBuf<uint32_t> b_counters;
+  DBuf<int32_t> b_candpos;
+  uint32_t fail_cap = 8;
+  std::vector<OpMeta> metas;            // per device op
+  std::vector<int> user_first_op;       // per caller op: index of its FILTER/RELEASE device op
+  std::vector<int> user_status;
+  std::vector<std::string> cand_names;  // explicit candidate list of the last hs_filter
+  std::vector<int> cand_slot;
+  bool have_cand = false;
+  std::vector<DevFail> fail_host;       // drained fail records: [slot][cap_nodes]
+  std::vector<uint32_t> op_fail_slot;   // per device op: slot in fail_host or ~0
+
+  // mask cache
+  std::unordered_map<std::string, std::array<uint64_t, 4>> mask_cache;
+  size_t mask_cache_types = 0;
+
+  // result arena (valid until the next call)
+  std::deque<std::string> r_strs;
+  std::vector<hs_alloc_entry> r_entries;
+  std::vector<hs_kv> r_annos;
+  std::vector<hs_failed_node> r_failed;
+  std::map<std::array<uint32_t, 3>, std::string> reason_cache;
+
+  const char* keep(const std::string& s) { r_strs.push_back(s); return r_strs.back().c_str(); }
+};
+
+namespace {
+
+#define CUDA_OK(h, call)                                                                      \
+  do {                                                                                        \
+    cudaError_t _e = (call);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      (h)->err = std::string(#call) + ": " + cudaGetErrorString(_e);                          \
+      return HS_ERR_CUDA;                                                                     \
+    }                                                                                         \
+  } while (0)
+
+static const char* kReasonNames[HS_R_COUNT] = {
+    "CardTypeMismatch", "CardUuidMismatch", "CardTimeSlicingExhausted", "CardComputeUnitsExhausted",
+    "CardInsufficientMemory", "CardInsufficientCore", "CardNotHealth", "CardCordoned", "NumaNotFit",
+    "ExclusiveDeviceAllocateConflict", "CardNotFoundCustomFilterRule", "CardMigTopologyInfeasible",
+    "AllocatedCardsInsufficientRequest", "ResourceQuotaNotFit", "ModeNotFit"};
+
+void add_vendor(hs_handle* h, const std::string& word, bool ascend) {
+  VendorInfo v;
+  v.id = (int)h->vendors.size();
+  v.word = word;
+  v.ascend = ascend;
+  if (word == "NVIDIA") {
+    v.use_type = "nvidia.com/use-gputype"; v.nouse_type = "nvidia.com/nouse-gputype";
+    v.use_uuid = "nvidia.com/use-gpuuuid"; v.nouse_uuid = "nvidia.com/nouse-gpuuuid";
+    v.to_allocate = "hami.io/vgpu-devices-to-allocate"; v.allocated = "hami.io/vgpu-devices-allocated";
+  } else if (word == "DCU") {
+    v.use_type = "hygon.com/use-dcutype"; v.nouse_type = "hygon.com/nouse-dcutype";
+    v.use_uuid = "hygon.com/use-gpuuuid"; v.nouse_uuid = "hygon.com/nouse-gpuuuid";
+    v.to_allocate = "hami.io/dcu-devices-to-allocate"; v.allocated = "hami.io/dcu-devices-allocated";
+  } else if (word == "MLU") {
+    v.use_uuid = "cambricon.com/use-gpuuuid"; v.nouse_uuid = "cambricon.com/nouse-gpuuuid";
+    v.to_allocate = "hami.io/cambricon-mlu-devices-to-allocate"; v.allocated = "hami.io/cambricon-mlu-devices-allocated";
+  } else {
+    v.use_uuid = "hami.io/use-" + word + "-uuid"; v.nouse_uuid = "hami.io/no-use-" + word + "-uuid";
+    v.to_allocate = "hami.io/" + word + "-devices-to-allocate"; v.allocated = "hami.io/" + word + "-devices-allocated";
+    v.ascend910 = word.compare(0, 9, "Ascend910") == 0;
+  }
+  h->vendor_by_word[word] = v.id;
+  h->vendors.push_back(v);
+}
+
+int intern_type(hs_handle* h, const std::string& t) {
+  auto it = h->type_ids.find(t);
+  if (it != h->type_ids.end()) return it->second;
+  if (h->types.size() >= HS_MAX_TYPES) return -1;
+  int id = (int)h->types.size();
+  h->types.push_back(t);
+  h->types_lower.push_back(lower(t));
+  h->types_upper.push_back(upper(t));
+  h->type_ids[t] = id;
+  return id;
+}
+
+int intern_mode(hs_handle* h, const std::string& m) {
+  for (size_t i = 0; i < h->modes.size(); i++) if (h->modes[i] == m) return (int)i;
+  if (h->modes.size() >= 8) return -1;
+  h->modes.push_back(m);
+  return (int)h->modes.size() - 1;
+}
+
+int grow_inventory(hs_handle* h, int need_nodes) {
+  if (need_nodes <= h->cap_nodes) return HS_OK;
+  int ncap = std::max(need_nodes, h->cap_nodes * 2);
+  ncap = (ncap + HS_TILE - 1) / HS_TILE * HS_TILE;
+  if (ncap < HS_TILE) ncap = HS_TILE;
+  int4 *nd = nullptr, *ns = nullptr; uint32_t* nf = nullptr; int16_t* np = nullptr;
+  CUDA_OK(h, cudaMalloc(&nd, (size_t)ncap * HS_D * sizeof(int4)));
+  CUDA_OK(h, cudaMalloc(&ns, (size_t)ncap * HS_D * sizeof(int4)));
+  CUDA_OK(h, cudaMalloc(&nf, (size_t)ncap * sizeof(uint32_t)));
+  CUDA_OK(h, cudaMalloc(&np, (size_t)ncap * 64 * sizeof(int16_t)));
+  if (h->d_dyn) { cudaFree(h->d_dyn); cudaFree(h->d_stat); cudaFree(h->d_flags); cudaFree(h->d_pair); }
+  h->d_dyn = nd; h->d_stat = ns; h->d_flags = nf; h->d_pair = np;
+  h->h_dyn.resize((size_t)ncap * HS_D, make_int4(0, 0, 0, 0));
+  h->h_stat.resize((size_t)ncap * HS_D, make_int4(0, 0, 0, 0));
+  h->h_flags.resize((size_t)ncap, 0u);
+  h->h_pair.resize((size_t)ncap * 64, (int16_t)0);
+  h->cap_nodes = ncap;
+  h->dirty_lo = 0;
+  h->dirty_hi = ncap / HS_TILE - 1;
+  return HS_OK;
+}
+
+inline size_t inv_idx(int node, int d) { return ((size_t)(node / HS_TILE) * HS_D + d) * HS_TILE + (node % HS_TILE); }
+
+void mark_dirty(hs_handle* h, int node) {
+  int t = node / HS_TILE;
+  h->dirty_lo = std::min(h->dirty_lo, t);
+  h->dirty_hi = std::max(h->dirty_hi, t);
+}
+
+int flush_inventory(hs_handle* h) {
+  if (h->dirty_hi < h->dirty_lo) return HS_OK;
+  size_t t0 = (size_t)h->dirty_lo, nt = (size_t)(h->dirty_hi - h->dirty_lo + 1);
+  size_t o = t0 * HS_D * HS_TILE, n = nt * HS_D * HS_TILE;
+  CUDA_OK(h, cudaMemcpyAsync(h->d_dyn + o, h->h_dyn.data() + o, n * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, cudaMemcpyAsync(h->d_stat + o, h->h_stat.data() + o, n * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, cudaMemcpyAsync(h->d_flags + t0 * HS_TILE, h->h_flags.data() + t0 * HS_TILE, nt * HS_TILE * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, cudaMemcpyAsync(h->d_pair + t0 * HS_TILE * 64, h->h_pair.data() + t0 * HS_TILE * 64, nt * HS_TILE * 64 * sizeof(int16_t), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, cudaStreamSynchronize(h->stream));  // the pageable host vectors may be resized right after
+  h->dirty_lo = 1 << 30;
+  h->dirty_hi = -1;
+  return HS_OK;
+}
+
+const std::string* find_anno(const hs_pod* pod, const char* key) {
+  static thread_local std::string tmp;
+  for (uint32_t i = 0; i < pod->n_annotations; i++) {
+    if (pod->annotations[i].key && strcmp(pod->annotations[i].key, key) == 0) {
+      tmp = pod->annotations[i].value ? pod->annotations[i].value : "";
+      return &tmp;
+    }
+  }
+  return nullptr;
+}
+bool get_anno(const hs_pod* pod, const std::string& key, std::string& out) {
+  if (key.empty()) return false;
+  // Go map semantics: a later duplicate key replaces an earlier one
+  bool found = false;
+  for (uint32_t i = 0; i < pod->n_annotations; i++)
+    if (pod->annotations[i].key && key == pod->annotations[i].key) {
+      out = pod->annotations[i].value ? pod->annotations[i].value : "";
+      found = true;
+    }
+  return found;
+}
+
+// masks over the interned device types for one (k.Type, selector annotations) combination
+std::array<uint64_t, 4> entry_masks(hs_handle* h, const VendorInfo* v, const std::string& ktype, const hs_pod* pod) {
+  if (h->mask_cache_types != h->types.size()) { h->mask_cache.clear(); h->mask_cache_types = h->types.size(); }
+  std::string use, nouse, mode;
+  bool hu = false, hn = false, hm = false;
+  if (v) {
+    hu = get_anno(pod, v->use_type, use);
+    hn = get_anno(pod, v->nouse_type, nouse);
+    if (v->word == "NVIDIA") hm = get_anno(pod, "nvidia.com/vgpu-mode", mode);
+  }
+  std::string key = ktype;
+  key += '\x1f'; key += v ? v->word : "?";
+  key += '\x1f'; if (hu) { key += '1'; key += use; }
+  key += '\x1f'; if (hn) { key += '1'; key += nouse; }
+  key += '\x1f'; if (hm) { key += '1'; key += mode; }
+  auto it = h->mask_cache.find(key);
+  if (it != h->mask_cache.end()) return it->second;
+  std::array<uint64_t, 4> m = {0, 0, 0, 0};
+  std::string kl = lower(ktype);
+  for (size_t t = 0; t < h->types.size(); t++) {
+    if (h->types_lower[t].find(kl) != std::string::npos) m[0] |= 1ull << t;   // getNodeResources, score.go:43-52
+    if (h->types[t] == ktype) m[1] |= 1ull << t;                              // gpu_policy.go:203
+    bool allow = true;
+    if (v && !v->use_type.empty()) allow = checkType(hu ? &use : nullptr, hn ? &nouse : nullptr, h->types_upper[t]);
+    if (allow) m[2] |= 1ull << t;
+  }
+  uint64_t modes = 0xffull;
+  if (hm) {  // nvidia/device.go:495-498: ok && !strings.Contains(mode, d.Mode) → mismatch
+    modes = 0;
+    for (size_t i = 0; i < h->modes.size(); i++) if (mode.find(h->modes[i]) != std::string::npos) modes |= 1ull << i;
+  }
+  m[3] = modes;
+  h->mask_cache[key] = m;
+  return m;
+}
+
+// use/no-use UUID annotation → sorted (node<<8 | mask8) words appended to the pool
+void uuid_words(hs_handle* h, const std::string& list, std::vector<uint32_t>& pool, uint32_t& off, uint32_t& cnt) {
+  std::map<uint32_t, uint32_t> per_node;
+  for (auto& u0 : splitComma(list)) {
+    std::string u = trimSpace(u0);
+    auto it = h->uuid_index.find(u);
+    if (it == h->uuid_index.end()) continue;
+    for (uint32_t w : it->second) per_node[w >> 8] |= 1u << (w & 255u);
+  }
+  off = (uint32_t)pool.size();
+  for (auto& kv : per_node) pool.push_back((kv.first << 8) | (kv.second & 255u));
+  cnt = (uint32_t)per_node.size();
+}
+
+struct Compiled {
+  DevPod pod;
+  std::vector<DevEntry> entries;
+  OpMeta meta;
+  uint32_t max_alloc = 0;
+};
+
+// Everything Filter derives from the pod before it looks at a node: Resourcereqs' output,
+// the per-pod knobs (score.go:139-146,361-364; util.go:277-285; scheduler.go:641-652) and
+// the selector annotations, flattened to integers.
+int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_pool, Compiled& c) {
+  memset(&c.pod, 0, sizeof c.pod);
+  c.entries.clear();
+  c.meta = OpMeta();
+  c.max_alloc = 0;
+  c.meta.uid = pod->uid ? pod->uid : "";
+  c.meta.n_ctr = (int)pod->n_containers;
+  c.meta.n_init = (int)std::min(pod->n_init, pod->n_containers);
+  bool any = false;
+  for (uint32_t i = 0; i < pod->n_containers; i++) if (pod->containers[i].n_reqs > 0) any = true;
+  if (!any) { c.meta.status = HS_PASSTHROUGH; return HS_PASSTHROUGH; }
+  if (pod->n_containers > HS_MAX_C) { h->err = "pod has more containers than HS_MAX_CONTAINERS"; return HS_ERR_UNSUPPORTED; }
+
+  std::string tmp;
+  std::string gpuPolicy = h->gpu_policy, nodePolicy = h->node_policy;
+  if (get_anno(pod, "hami.io/gpu-scheduler-policy", tmp)) gpuPolicy = tmp;
+  if (get_anno(pod, "hami.io/node-scheduler-policy", tmp)) nodePolicy = tmp;
+  bool numaBind = get_anno(pod, "nvidia.com/numa-bind", tmp) && parseBoolTrue(tmp);
+  int64_t w[3] = {1, 1, 1};
+  if (get_anno(pod, "hami.io/device-scoring-weights", tmp)) {
+    if (!parseWeights(tmp, w)) { h->err = "invalid hami.io/device-scoring-weights annotation"; return HS_ERR_WEIGHTS; }
+  }
+  DevPod& p = c.pod;
+  p.op = OP_FILTER;
+  p.w_slot = (float)w[0]; p.w_core = (float)w[1]; p.w_mem = (float)w[2];
+  if (nodePolicy == "spread") p.flags |= PF_NODE_SPREAD;
+  if (policyContains(gpuPolicy, "mutex")) p.flags |= PF_MUTEX;
+  if (policyContains(gpuPolicy, "topology-aware")) p.flags |= PF_TOPOLOGY;
+  if (numaBind) p.flags |= PF_NUMA_ASSERT;
+  if (get_anno(pod, "huawei.com/vnpu-mode", tmp)) { c.meta.vnpu_mode = tmp; if (tmp == "hami-core") p.flags |= PF_ASCEND_HAMICORE; }
+  // comparator, policy/gpu_policy.go:77-167
+  if (gpuPolicy.find(',') != std::string::npos || gpuPolicy == "numa") {
+    p.sort_mode = SORT_CHAIN;
+    std::vector<int> chain;
+    bool seen[4] = {false, false, false, false};
+    for (auto& t0 : splitComma(gpuPolicy)) {
+      std::string t = trimSpace(t0);
+      int k = t == "binpack" ? CK_BINPACK : t == "spread" ? CK_SPREAD : t == "numa" ? CK_NUMA : CK_NONE;
+      if (k != CK_NONE && !seen[k]) { chain.push_back(k); seen[k] = true; }
+    }
+    if (chain.empty()) chain.push_back(CK_SPREAD);
+    if (numaBind && chain[0] != CK_NUMA) {
+      std::vector<int> withNuma = {CK_NUMA};
+      for (int k : chain) if (k != CK_NUMA) withNuma.push_back(k);
+      chain = withNuma;
+    }
+    for (size_t i = 0; i < 3; i++) p.chain[i] = i < chain.size() ? (uint8_t)chain[i] : (uint8_t)CK_NONE;
+  } else if (gpuPolicy == "mutex") {
+    p.sort_mode = SORT_MUTEX;
+  } else if (numaBind) {
+    p.sort_mode = gpuPolicy == "binpack" ? SORT_NUMA_BINPACK : SORT_NUMA_SPREAD;
+  } else {
+    p.sort_mode = gpuPolicy == "binpack" ? SORT_BINPACK : SORT_SPREAD;
+  }
+  std::string vgpuMode;
+  bool hasVgpuMode = get_anno(pod, "nvidia.com/vgpu-mode", vgpuMode);
+
+  p.n_ctr = (uint8_t)pod->n_containers;
+  p.n_init = (uint8_t)c.meta.n_init;
+  std::set<std::string> keyset, slotset;
+  c.meta.ctr_begin.assign(pod->n_containers + 1, 0);
+  for (uint32_t ci = 0; ci < pod->n_containers; ci++) {
+    // ContainerDeviceRequests is a map: later duplicate keys replace earlier ones; canonical rule 4: sorted keys
+    std::map<std::string, const hs_container_request*> m;
+    for (uint32_t r = 0; r < pod->containers[ci].n_reqs; r++) {
+      const hs_container_request* q = &pod->containers[ci].reqs[r];
+      m[q->key ? q->key : ""] = q;
+    }
+    p.ctr_begin[ci] = (uint8_t)c.entries.size();
+    c.meta.ctr_begin[ci] = (uint8_t)c.entries.size();
+    for (auto& kv : m) {
+      const hs_container_request* q = kv.second;
+      if (c.entries.size() >= HS_MAX_E) { h->err = "pod has more request entries than HS_MAX_REQS_PER_POD"; return HS_ERR_UNSUPPORTED; }
+      DevEntry e;
+      memset(&e, 0, sizeof e);
+      std::string ktype = q->type ? q->type : "";
+      e.nums = q->nums; e.memreq = q->memreq; e.mempct = q->mempct; e.coresreq = q->coresreq;
+      auto vit = h->vendor_by_word.find(ktype);
+      const VendorInfo* v = vit == h->vendor_by_word.end() ? nullptr : &h->vendors[vit->second];
+      e.vendor = v ? (uint16_t)v->id : (uint16_t)HV_NONE;
+      auto masks = entry_masks(h, v, ktype, pod);
+      e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
+      if (v && v->ascend910) e.flags |= EF_ASCEND910;
+      if (v && v->ascend && ktype == "Ascend910C") e.flags |= EF_ASCEND910C;
+      if (!hasVgpuMode || vgpuMode.find("mig") != std::string::npos) e.flags |= EF_MIGMODE_OK;
+      e.score_slot = -1;
+      e.is_init = ci < (uint32_t)c.meta.n_init ? 1 : 0;
+      if (v) {
+        std::string list;
+        if (get_anno(pod, v->use_uuid, list) && !trimSpace(list).empty()) {
+          e.has_use = 1;
+          uuid_words(h, list, uuid_pool, e.use_off, e.use_cnt);
+        }
+        if (get_anno(pod, v->nouse_uuid, list) && !trimSpace(list).empty())
+          uuid_words(h, list, uuid_pool, e.nouse_off, e.nouse_cnt);
+      }
+      keyset.insert(ktype);
+      if (v && v->ascend910) slotset.insert(ktype);
+      c.entries.push_back(e);
+      c.meta.entries.push_back(EntryMeta{ktype, (int)ci, v ? v->id : -1});
+      int nn = q->nums < 0 ? 0 : (q->nums > HS_D ? HS_D : q->nums);
+      c.max_alloc += (uint32_t)nn;
+    }
+  }
+  p.ctr_begin[pod->n_containers] = (uint8_t)c.entries.size();
+  c.meta.ctr_begin[pod->n_containers] = (uint8_t)c.entries.size();
+  p.n_entries = (uint8_t)c.entries.size();
+  if (slotset.size() > HS_SCORE_SLOTS) { h->err = "pod names more Ascend910 types than HS_SCORE_SLOTS"; return HS_ERR_UNSUPPORTED; }
+  if (c.max_alloc > HS_MAX_ALLOC) { h->err = "pod asks for more devices than HS_MAX_ALLOC"; return HS_ERR_UNSUPPORTED; }
+  for (size_t i = 0; i < c.entries.size(); i++) {
+    const std::string& t = c.meta.entries[i].type;
+    c.entries[i].key_id = (uint8_t)std::distance(keyset.begin(), keyset.find(t));
+    auto s = slotset.find(t);
+    if (s != slotset.end()) c.entries[i].score_slot = (int8_t)std::distance(slotset.begin(), s);
+  }
+  c.meta.kind = OP_FILTER;
+  c.meta.status = HS_OK;
+  return HS_OK;
+}
+
+void apply_host_delta(hs_handle* h, int node, const int4* delta, int sign) {
+  for (int d = 0; d < HS_D; d++) {
+    int4& v = h->h_dyn[inv_idx(node, d)];
+    v.x += sign * delta[d].x; v.y += sign * delta[d].y; v.z += sign * delta[d].z;
+  }
+}
+
+std::string encode_pod_single(const std::vector<std::vector<const hs_alloc_entry*>>& pd) {
+  // EncodePodSingleDevice / EncodeContainerDevices, devices.go:451-484
+  std::string res;
+  char buf[64];
+  for (auto& ctr : pd) {
+    for (auto* e : ctr) {
+      res += e->uuid; res += ','; res += e->type_key;
+      snprintf(buf, sizeof buf, ",%d,%d:", e->usedmem, e->usedcores);
+      res += buf;
+    }
+    res += ';';
+  }
+  return res;
+}
+
+const std::string& fail_string(hs_handle* h, const DevFail& f) {
+  std::array<uint32_t, 3> key = {f.kind_cards, f.c0, f.c1};
+  auto it = h->reason_cache.find(key);
+  if (it != h->reason_cache.end()) return it->second;
+  std::string s;
+  uint32_t kind = f.kind_cards & 15u, cards = f.kind_cards >> 4;
+  if (kind == FK_NODE_INSUFFICIENT) s = "NodeInsufficientDevice";
+  else if (kind == FK_TYPE_NOT_FOUND) s = "Device type not found";
+  else if (kind == FK_HIST) {
+    // common.GenReason, common/common.go:46-53
+    std::vector<std::string> parts;
+    char buf[96];
+    for (int r = 0; r < HS_R_COUNT; r++) {
+      uint32_t cnt = r < 8 ? (f.c0 >> (4 * r)) & 15u : (f.c1 >> (4 * (r - 8))) & 15u;
+      if (!cnt) continue;
+      snprintf(buf, sizeof buf, "%u/%u %s", cnt, cards, kReasonNames[r]);
+      parts.push_back(buf);
+    }
+    std::sort(parts.begin(), parts.end());
+    for (size_t i = 0; i < parts.size(); i++) { if (i) s += ", "; s += parts[i]; }
+  }
+  return h->reason_cache[key] = s;
+}
+
+int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_cap) {
+  memset(&ka, 0, sizeof ka);
+  ka.dyn = h->d_dyn; ka.stat = h->d_stat; ka.node_flags = h->d_flags; ka.pair = h->d_pair;
+  ka.n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
+  ka.cand_pos = h->have_cand ? h->b_candpos.d : nullptr;
+  ka.pods = h->b_pods.d; ka.entries = h->b_entries.d; ka.uuid_pool = h->b_uuid.d; ka.rel_pool = h->b_rel.d;
+  ka.n_ops = n_ops;
+  ka.decisions = h->b_dec.d; ka.allocs = h->b_alloc.d; ka.alloc_cap = alloc_cap;
+  ka.commit_delta = h->b_delta.d; ka.best = h->b_best.d;
+  ka.fail = h->b_fail.d; ka.fail_cap = h->fail_cap;
+  ka.counters = h->b_counters.d;
+  ka.pos_base = 0;
+  return HS_OK;
+}
+
+// Run the device ops [0, n) staged in the b_* host mirrors; drains the fail buffer and resumes
+// until every op ran.  On return b_dec.h / b_alloc.h / b_delta.h hold the results.
+int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, size_t n_rel, uint32_t alloc_cap) {
+  int rc = flush_inventory(h);
+  if (rc != HS_OK) return rc;
+  const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
+  if (!h->b_dec.ensure(n_ops) || !h->b_alloc.ensure(std::max<uint32_t>(alloc_cap, 1)) || !h->b_delta.ensure((size_t)n_ops * HS_D) ||
+      !h->b_best.ensure(n_ops) || !h->b_counters.ensure(8) || !h->b_fail.ensure((size_t)h->fail_cap * std::max(n_nodes, HS_TILE))) {
+    h->err = "out of device memory for batch buffers";
+    return HS_ERR_CUDA;
+  }
+  CUDA_OK(h, cudaMemcpyAsync(h->b_pods.d, h->b_pods.h, (size_t)n_ops * sizeof(DevPod), cudaMemcpyHostToDevice, h->stream));
+  if (n_entries) CUDA_OK(h, cudaMemcpyAsync(h->b_entries.d, h->b_entries.h, n_entries * sizeof(DevEntry), cudaMemcpyHostToDevice, h->stream));
+  if (n_uuid) CUDA_OK(h, cudaMemcpyAsync(h->b_uuid.d, h->b_uuid.h, n_uuid * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+  if (n_rel) CUDA_OK(h, cudaMemcpyAsync(h->b_rel.d, h->b_rel.h, n_rel * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+  if (h->have_cand) CUDA_OK(h, cudaMemcpyAsync(h->b_candpos.d, h->b_candpos.h, (size_t)n_nodes * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, cudaMemsetAsync(h->b_dec.d, 0xff, (size_t)n_ops * sizeof(DevDecision), h->stream));
+  CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, (size_t)n_ops * sizeof(unsigned long long), h->stream));
+  CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
+
+  int block = h->block;
+  int maxb = hs_decide_max_blocks(block, h->device);
+  if (maxb <= 0) { h->err = "hs_decide_kernel cannot be launched cooperatively on this device"; return HS_ERR_CUDA; }
+  int grid = std::min(maxb, std::max(1, (n_nodes + block - 1) / block));
+
+  h->fail_host.clear();
+  h->op_fail_slot.assign(n_ops, 0xffffffffu);
+  h->last_ms = 0;
+  int done = 0;
+  uint32_t alloc_base = 0;
+  while (done < n_ops) {
+    KernelArgs ka;
+    build_kernel_args(h, ka, n_ops, alloc_cap);
+    ka.op_begin = done;
+    CUDA_OK(h, cudaEventRecord(h->ev0, h->stream));
+    cudaError_t le = (cudaError_t)hs_launch_decide(&ka, grid, block, h->stream);
+    if (le != cudaSuccess) { h->err = std::string("hs_decide_kernel launch: ") + cudaGetErrorString(le); return HS_ERR_CUDA; }
+    h->launches++;
+    CUDA_OK(h, cudaEventRecord(h->ev1, h->stream));
+    CUDA_OK(h, cudaMemcpyAsync(h->b_counters.h, h->b_counters.d, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_OK(h, cudaStreamSynchronize(h->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    h->last_ms += ms;
+    uint32_t ran = h->b_counters.h[2] - (uint32_t)done, nfail = h->b_counters.h[1];
+    if (nfail) {
+      size_t base = h->fail_host.size();
+      h->fail_host.resize(base + (size_t)nfail * n_nodes);
+      CUDA_OK(h, cudaMemcpy(h->fail_host.data() + base, h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail), cudaMemcpyDeviceToHost));
+    }
+    if (ran == 0 && nfail == 0 && n_ops - done > 0) { h->err = "decide kernel made no progress"; return HS_ERR_CUDA; }
+    // decisions of this launch
+    CUDA_OK(h, cudaMemcpy(h->b_dec.h + done, h->b_dec.d + done, (size_t)ran * sizeof(DevDecision), cudaMemcpyDeviceToHost));
+    uint32_t slot_base = (uint32_t)(h->fail_host.size() / std::max(n_nodes, 1)) - nfail;
+    for (uint32_t i = 0; i < ran; i++) {
+      DevDecision& d = h->b_dec.h[done + i];
+      if (d.status == 1 && d.fail_slot != 0xffffffffu) h->op_fail_slot[done + i] = slot_base + d.fail_slot;
+    }
+    done += (int)ran;
+    alloc_base = h->b_counters.h[0];
+    if (done < n_ops) {
+      // resume: keep the alloc cursor, clear the fail cursor
+      h->b_counters.h[1] = 0; h->b_counters.h[2] = 0;
+      CUDA_OK(h, cudaMemcpyAsync(h->b_counters.d, h->b_counters.h, 8 * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    }
+  }
+  if (alloc_base) CUDA_OK(h, cudaMemcpy(h->b_alloc.h, h->b_alloc.d, (size_t)std::min(alloc_base, alloc_cap) * sizeof(DevAlloc), cudaMemcpyDeviceToHost));
+  CUDA_OK(h, cudaMemcpy(h->b_delta.h, h->b_delta.d, (size_t)n_ops * HS_D * sizeof(int4), cudaMemcpyDeviceToHost));
+  return HS_OK;
+}
+
+// Fill hs_filter_result for device op `op` (the chosen NodeScore, annotations or FailedNodes).
+void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
+  memset(out, 0, sizeof *out);
+  out->node_index = -1;
+  const OpMeta& m = h->metas[op];
+  if (m.status != HS_OK) { out->status = m.status; return; }
+  if (m.kind != OP_FILTER) { out->status = HS_OK; return; }
+  const DevDecision& dec = h->b_dec.h[op];
+  h->r_entries.clear(); h->r_annos.clear(); h->r_failed.clear();
+  if (dec.status == 0) {
+    const NodeSlot& ns = h->nodes[dec.node];
+    out->status = HS_FIT;
+    out->node_name = ns.name.c_str();
+    out->score = dec.score;
+    if (h->have_cand) {
+      out->node_index = h->b_candpos.h[dec.node];
+    } else if (!h->has_dead) {
+      out->node_index = dec.node;
+    } else {
+      int idx = 0;
+      for (int i = 0; i < dec.node; i++) if (h->nodes[i].alive) idx++;
+      out->node_index = idx;
+    }
+    // per entry: its rows
+    std::vector<std::vector<hs_alloc_entry>> rows(m.entries.size());
+    for (uint32_t i = 0; i < dec.n_alloc; i++) {
+      const DevAlloc& a = h->b_alloc.h[dec.alloc_off + i];
+      const EntryMeta& em = m.entries[a.entry];
+      const DevSlot& ds = ns.devs[a.dev];
+      rows[a.entry].push_back(hs_alloc_entry{0, em.type.c_str(), ds.uuid.c_str(), (int32_t)ds.index, a.usedmem, (int32_t)a.usedcores});
+    }
+    // scoreNode's PodDevices bookkeeping incl. the base-type padding (score.go:226-286,334-338)
+    typedef std::vector<std::vector<hs_alloc_entry>> PSD;
+    std::map<std::string, PSD> pd, initAllocs;
+    for (int c = 0; c < m.n_init && c < m.n_ctr; c++) {
+      int eb = m.ctr_begin[c], ee = m.ctr_begin[c + 1];
+      if (eb == ee) { for (auto& t : ns.base_types) initAllocs[t].push_back({}); continue; }
+      for (int e = eb; e < ee; e++) initAllocs[m.entries[e].type].push_back(rows[e]);
+      for (auto& t : ns.base_types) if ((int)initAllocs[t].size() == c) initAllocs[t].push_back({});
+    }
+    int appIndex = 0;
+    for (int c = m.n_init; c < m.n_ctr; c++) {
+      int eb = m.ctr_begin[c], ee = m.ctr_begin[c + 1];
+      // sums == 0 → pad only (score.go:262-272); the compiled entries keep the caller's nums
+      int sums = 0;
+      for (int e = eb; e < ee; e++) sums += h->b_entries.h[h->b_pods.h[op].entry_off + e].nums;
+      if (sums == 0) { for (auto& t : ns.base_types) pd[t].push_back({}); appIndex++; continue; }
+      for (int e = eb; e < ee; e++) pd[m.entries[e].type].push_back(rows[e]);
+      for (auto& t : ns.base_types) if ((int)pd[t].size() == appIndex) pd[t].push_back({});
+      appIndex++;
+    }
+    if (m.n_init > 0)
+      for (auto& kv : initAllocs) {
+        PSD merged = kv.second;
+        PSD& cur = pd[kv.first];
+        merged.insert(merged.end(), cur.begin(), cur.end());
+        cur = merged;
+      }
+    // flatten (uuid == NULL marks an empty ContainerDevices at that position)
+    std::map<std::string, std::vector<std::vector<const hs_alloc_entry*>>> views;
+    size_t total = 0;
+    for (auto& kv : pd) for (auto& c : kv.second) total += c.empty() ? 1 : c.size();
+    h->r_entries.reserve(total);
+    for (auto& kv : pd) {
+      const char* key = h->keep(kv.first);
+      auto& view = views[kv.first];
+      view.resize(kv.second.size());
+      for (size_t c = 0; c < kv.second.size(); c++) {
+        if (kv.second[c].empty()) { h->r_entries.push_back(hs_alloc_entry{(uint32_t)c, key, nullptr, 0, 0, 0}); continue; }
+        for (auto& e : kv.second[c]) {
+          hs_alloc_entry x = e;
+          x.container = (uint32_t)c;
+          x.type_key = key;
+          h->r_entries.push_back(x);
+          view[c].push_back(&h->r_entries.back());
+        }
+      }
+    }
+    // annotations: scheduler.go:1124-1130 + each vendor's PatchAnnotations
+    std::map<std::string, std::string> annos;
+    annos["hami.io/vgpu-node"] = ns.name;
+    annos["hami.io/vgpu-time"] = "";
+    for (auto& v : h->vendors) {
+      auto it = views.find(v.word);
+      if (it == views.end() || it->second.empty()) continue;
+      std::string s = encode_pod_single(it->second);
+      if (v.word == "MLU") {  // cambricon/device.go:312-332
+        annos["CAMBRICON_DSMLU_ASSIGNED"] = "false";
+        for (auto& ctr : it->second)
+          if (!ctr.empty()) {
+            char buf[64];
+            snprintf(buf, sizeof buf, "%d_%d_%d", ctr[0]->idx, ctr[0]->usedcores, ctr[0]->usedmem / 256);
+            annos["CAMBRICON_DSMLU_PROFILE"] = buf;
+            break;
+          }
+      }
+      annos[v.to_allocate] = s;
+      annos[v.allocated] = s;
+      if (v.ascend) {  // ascend/device.go:221-253
+        annos["predicate-time"] = "";
+        std::string json;
+        bool anyrow = false;
+        for (auto& ctr : it->second)
+          for (auto* e : ctr) {
+            std::string o = "{";
+            bool first = true;
+            auto add = [&](const std::string& f) { if (!first) o += ","; o += f; first = false; };
+            if (e->uuid && e->uuid[0]) add(std::string("\"UUID\":\"") + e->uuid + "\"");
+            if (m.vnpu_mode != "hami-core") {
+              std::string temp;
+              for (auto& t : v.templates) if ((int64_t)e->usedmem <= t.second) { temp = t.first; break; }
+              if (!temp.empty()) add("\"temp\":\"" + temp + "\"");
+            }
+            if (e->usedmem != 0) add("\"memory\":" + std::to_string((long long)e->usedmem));
+            if (e->usedcores != 0) add("\"core\":" + std::to_string(e->usedcores));
+            o += "}";
+            json += (anyrow ? "," : "") + o;
+            anyrow = true;
+          }
+        annos["huawei.com/" + v.word] = anyrow ? "[" + json + "]" : "null";
+      }
+    }
+    for (auto& kv : annos) h->r_annos.push_back(hs_kv{h->keep(kv.first), h->keep(kv.second)});
+  } else if (dec.status == 1) {
+    out->status = HS_NOFIT;
+    uint32_t slot = h->op_fail_slot[op];
+    const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
+    auto reason_of = [&](int node) -> const char* {
+      if (slot == 0xffffffffu) return "";
+      const DevFail& f = h->fail_host[(size_t)slot * n_nodes + node];
+      return fail_string(h, f).c_str();
+    };
+    if (h->have_cand) {
+      for (size_t i = 0; i < h->cand_names.size(); i++) {
+        int s = h->cand_slot[i];
+        if (s < 0) h->r_failed.push_back(hs_failed_node{h->cand_names[i].c_str(), "node unregistered"});
+        else h->r_failed.push_back(hs_failed_node{h->nodes[s].name.c_str(), reason_of(s)});
+      }
+    } else {
+      for (size_t s = 0; s < h->nodes.size(); s++)
+        if (h->nodes[s].alive) h->r_failed.push_back(hs_failed_node{h->nodes[s].name.c_str(), reason_of((int)s)});
+    }
+  } else {
+    out->status = HS_ERR_CUDA;
+  }
+  out->entries = h->r_entries.data(); out->n_entries = (uint32_t)h->r_entries.size();
+  out->annotations = h->r_annos.data(); out->n_annotations = (uint32_t)h->r_annos.size();
+  out->failed = h->r_failed.data(); out->n_failed = (uint32_t)h->r_failed.size();
+}
+
+// Stage a RELEASE device op for `uid` (pods map or an earlier FILTER of this batch).
+bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std::string, int>& in_batch,
+                   std::vector<DevPod>& pods, std::vector<int4>& rel, std::vector<OpMeta>& metas, int user_op) {
+  DevPod p;
+  memset(&p, 0, sizeof p);
+  p.op = OP_RELEASE;
+  auto ib = in_batch.find(uid);
+  if (ib != in_batch.end()) {
+    p.rel_node = -1;
+    p.rel_ref = ib->second;
+    in_batch.erase(ib);
+  } else {
+    auto it = h->pods.find(uid);
+    if (it == h->pods.end()) return false;
+    p.rel_node = it->second.node;
+    p.rel_off = (int32_t)rel.size();
+    for (int d = 0; d < HS_D; d++) rel.push_back(it->second.delta[d]);
+    h->pods.erase(it);
+  }
+  OpMeta m;
+  m.kind = OP_RELEASE;
+  m.uid = uid;
+  m.user_op = user_op;
+  pods.push_back(p);
+  metas.push_back(m);
+  return true;
+}
+
+// Apply the finished batch to the host mirrors: usage cache + podManager.
+void absorb_results(hs_handle* h, int n_ops) {
+  for (int op = 0; op < n_ops; op++) {
+    const OpMeta& m = h->metas[op];
+    const DevDecision& dec = h->b_dec.h[op];
+    if (m.kind == OP_FILTER && m.status == HS_OK && dec.status == 0) {
+      PodRec pr;
+      pr.node = dec.node;
+      for (int d = 0; d < HS_D; d++) pr.delta[d] = h->b_delta.h[(size_t)op * HS_D + d];
+      apply_host_delta(h, dec.node, pr.delta, +1);
+      h->pods[m.uid] = pr;
+    } else if (m.kind == OP_RELEASE) {
+      const DevPod& p = h->b_pods.h[op];
+      if (p.rel_node >= 0) {
+        apply_host_delta(h, p.rel_node, h->b_rel.h + p.rel_off, -1);
+      } else {
+        auto it = h->pods.find(m.uid);
+        if (it != h->pods.end()) { apply_host_delta(h, it->second.node, it->second.delta, -1); h->pods.erase(it); }
+      }
+    }
+  }
+}
+
+// Compile caller ops into device ops (implicit release of a pod that is filtered again,
+// scheduler.go:1092-1094), run them, absorb the results.
+int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
+  std::vector<DevPod> pods;
+  std::vector<DevEntry> entries;
+  std::vector<uint32_t> uuid_pool;
+  std::vector<int4> rel;
+  std::vector<OpMeta> metas;
+  std::unordered_map<std::string, int> in_batch;
+  h->user_first_op.assign(n_ops, -1);
+  h->user_status.assign(n_ops, HS_OK);
+  uint32_t alloc_cap = 0;
+  Compiled c;
+  for (uint32_t i = 0; i < n_ops; i++) {
+    const hs_pod* pod = ops[i].pod;
+    if (!pod || !pod->uid) { h->user_status[i] = HS_ERR_INVALID; continue; }
+    std::string uid = pod->uid;
+    if (ops[i].kind == HS_OP_DELETE) {
+      if (stage_release(h, uid, in_batch, pods, rel, metas, (int)i)) h->user_first_op[i] = (int)pods.size() - 1;
+      else h->user_status[i] = HS_ERR_NOTFOUND;
+      continue;
+    }
+    int rc = compile_pod(h, pod, uuid_pool, c);
+    if (rc != HS_OK) { h->user_status[i] = rc; continue; }
+    stage_release(h, uid, in_batch, pods, rel, metas, -1);  // TakeAndDeletePod
+    c.pod.entry_off = (uint32_t)entries.size();
+    entries.insert(entries.end(), c.entries.begin(), c.entries.end());
+    c.meta.user_op = (int)i;
+    pods.push_back(c.pod);
+    metas.push_back(c.meta);
+    in_batch[uid] = (int)pods.size() - 1;
+    h->user_first_op[i] = (int)pods.size() - 1;
+    alloc_cap += c.max_alloc;
+  }
+  h->metas.swap(metas);
+  int n = (int)pods.size();
+  if (n == 0) return HS_OK;
+  if (!h->b_pods.ensure(n) || !h->b_entries.ensure(std::max<size_t>(entries.size(), 1)) ||
+      !h->b_uuid.ensure(std::max<size_t>(uuid_pool.size(), 1)) || !h->b_rel.ensure(std::max<size_t>(rel.size(), 1))) {
+    h->err = "out of memory for batch staging";
+    return HS_ERR_CUDA;
+  }
+  memcpy(h->b_pods.h, pods.data(), (size_t)n * sizeof(DevPod));
+  if (!entries.empty()) memcpy(h->b_entries.h, entries.data(), entries.size() * sizeof(DevEntry));
+  if (!uuid_pool.empty()) memcpy(h->b_uuid.h, uuid_pool.data(), uuid_pool.size() * sizeof(uint32_t));
+  if (!rel.empty()) memcpy(h->b_rel.h, rel.data(), rel.size() * sizeof(int4));
+  int rc = run_device_ops(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap);
+  if (rc != HS_OK) return rc;
+  absorb_results(h, n);
+  return HS_OK;
+}
+
+}  // namespace
+
+// ================================================================================================
+extern "C" {
+
+hs_handle* hs_create(const hs_config* cfg) {
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    g_create_error = std::string("hs_create: no usable CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") +
+                     "); this engine has no CPU fallback";
+    return nullptr;
+  }
+  hs_handle* h = new hs_handle();
+  if (cfg) {
+    if (cfg->node_scheduler_policy) h->node_policy = cfg->node_scheduler_policy;
+    if (cfg->gpu_scheduler_policy) h->gpu_policy = cfg->gpu_scheduler_policy;
+    h->ascend_vnpu_default = cfg->ascend_hami_vnpu_core != 0;
+  }
+  int dev = cfg && cfg->cuda_device >= 0 ? cfg->cuda_device : -1;
+  if (dev < 0) cudaGetDevice(&dev);
+  h->device = dev;
+  if (cudaSetDevice(dev) != cudaSuccess || cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess) {
+    g_create_error = std::string("hs_create: ") + cudaGetErrorString(cudaGetLastError());
+    delete h;
+    return nullptr;
+  }
+  add_vendor(h, "NVIDIA", false);
+  add_vendor(h, "DCU", false);
+  add_vendor(h, "MLU", false);
+  if (cfg)
+    for (uint32_t i = 0; i < cfg->n_ascend && h->vendors.size() < 15; i++) {
+      add_vendor(h, cfg->ascend[i].common_word ? cfg->ascend[i].common_word : "", true);
+      VendorInfo& v = h->vendors.back();
+      for (uint32_t t = 0; t < cfg->ascend[i].n_templates; t++)
+        v.templates.push_back({cfg->ascend[i].templates[t].name ? cfg->ascend[i].templates[t].name : "", cfg->ascend[i].templates[t].memory});
+      std::stable_sort(v.templates.begin(), v.templates.end(),
+                       [](const std::pair<std::string, int64_t>& a, const std::pair<std::string, int64_t>& b) { return a.second < b.second; });
+    }
+  h->modes = {"", "hami-core", "mig", "mps"};
+  const char* blk = getenv("HS_BLOCK");
+  if (blk) { int b = atoi(blk); if (b == 32 || b == 64 || b == 128) h->block = b; }
+  const char* fc = getenv("HS_FAIL_CAP");
+  if (fc && atoi(fc) > 0) h->fail_cap = (uint32_t)atoi(fc);
+  if (grow_inventory(h, cfg && cfg->reserve_nodes ? (int)cfg->reserve_nodes : HS_TILE) != HS_OK) {
+    g_create_error = h->err;
+    delete h;
+    return nullptr;
+  }
+  return h;
+}
+
+void hs_destroy(hs_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->d_dyn) { cudaFree(h->d_dyn); cudaFree(h->d_stat); cudaFree(h->d_flags); cudaFree(h->d_pair); }
+  h->b_pods.release(); h->b_entries.release(); h->b_uuid.release(); h->b_rel.release(); h->b_dec.release();
+  h->b_alloc.release(); h->b_delta.release(); h->b_best.release(); h->b_fail.release(); h->b_counters.release();
+  h->b_candpos.release();
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+const char* hs_last_error(const hs_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int32_t hs_node_count(const hs_handle* h) { return h->n_alive; }
+
+int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
+  if (!h || !node || !node->name) return HS_ERR_INVALID;
+  if (node->n_devices > HS_MAX_DEVICES_PER_NODE) { h->err = "node has more devices than HS_MAX_DEVICES_PER_NODE"; return HS_ERR_UNSUPPORTED; }
+  std::vector<DevSlot> devs;
+  for (uint32_t i = 0; i < node->n_devices; i++) {
+    const hs_device_info& d = node->devices[i];
+    DevSlot s;
+    s.uuid = d.id ? d.id : ""; s.type = d.type ? d.type : ""; s.mode = d.mode ? d.mode : ""; s.vendor = d.vendor ? d.vendor : "";
+    s.index = d.index; s.count = d.count; s.devmem = d.devmem; s.devcore = d.devcore; s.numa = d.numa;
+    s.network_id = d.network_id; s.health = d.health != 0;
+    if (s.mode == "mig") { h->err = "MIG-mode devices are outside the built scope (dynamic MIG placement)"; return HS_ERR_UNSUPPORTED; }
+    if (s.numa < 0 || s.numa > 255 || s.index > 255 || s.network_id > 254) { h->err = "numa/index/NetworkID out of the packed range"; return HS_ERR_UNSUPPORTED; }
+    s.type_id = intern_type(h, s.type);
+    if (s.type_id < 0) { h->err = "more distinct device types than HS_MAX_TYPES"; return HS_ERR_UNSUPPORTED; }
+    s.mode_id = intern_mode(h, s.mode);
+    if (s.mode_id < 0) { h->err = "more distinct device modes than supported"; return HS_ERR_UNSUPPORTED; }
+    auto v = h->vendor_by_word.find(s.vendor);
+    s.vendor_id = v == h->vendor_by_word.end() ? HV_NONE : v->second;
+    devs.push_back(s);
+  }
+  // canonical rule 5: vendors in sorted key order, registration order inside a vendor
+  std::vector<int> perm(devs.size());
+  for (size_t i = 0; i < perm.size(); i++) perm[i] = (int)i;
+  std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return devs[a].vendor < devs[b].vendor; });
+  std::vector<DevSlot> sorted;
+  for (int i : perm) sorted.push_back(devs[i]);
+
+  int slot;
+  auto it = h->node_by_name.find(node->name);
+  if (it == h->node_by_name.end()) {
+    slot = (int)h->nodes.size();
+    int rc = grow_inventory(h, slot + 1);
+    if (rc != HS_OK) return rc;
+    h->nodes.emplace_back();
+    h->nodes[slot].name = node->name;
+    h->node_by_name[node->name] = slot;
+  } else {
+    slot = it->second;
+  }
+  NodeSlot& ns = h->nodes[slot];
+  // keep committed usage of surviving UUIDs; drop index entries of the old devices
+  std::unordered_map<std::string, int4> old_usage;
+  for (size_t d = 0; d < ns.devs.size(); d++) {
+    old_usage[ns.devs[d].uuid] = h->h_dyn[inv_idx(slot, (int)d)];
+    auto& vec = h->uuid_index[ns.devs[d].uuid];
+    vec.erase(std::remove(vec.begin(), vec.end(), ((uint32_t)slot << 8) | (uint32_t)d), vec.end());
+    if (vec.empty()) h->uuid_index.erase(ns.devs[d].uuid);
+  }
+  if (!ns.alive) { h->n_alive++; }
+  ns.alive = true;
+  ns.devs = sorted;
+  ns.has_cordon = node->device_cordon != nullptr;
+  ns.cordon = node->device_cordon ? node->device_cordon : "";
+  ns.vnpu = node->hami_vnpu_core;
+  std::set<std::string> bt;
+  for (auto& d : ns.devs) bt.insert(d.type);
+  ns.base_types.assign(bt.begin(), bt.end());
+  std::set<std::string> cordoned;  // cordonedDevices, nvidia/device.go:698-713
+  if (ns.has_cordon && !trimSpace(ns.cordon).empty())
+    for (auto& u0 : splitComma(ns.cordon)) { std::string u = trimSpace(u0); if (!u.empty()) cordoned.insert(u); }
+
+  bool uniform = true;
+  int uval = 0; bool have = false;
+  const int n = (int)ns.devs.size();
+  for (int d = 0; d < HS_D; d++) {
+    int4 dy = make_int4(0, 0, 0, 0), st = make_int4(0, 0, 0, 0);
+    if (d < n) {
+      const DevSlot& s = ns.devs[d];
+      auto ou = old_usage.find(s.uuid);
+      if (ou != old_usage.end()) { dy.x = ou->second.x; dy.y = ou->second.y; dy.z = ou->second.z; }
+      uint32_t df = DF_PRESENT | (s.health ? DF_HEALTH : 0u) | (cordoned.count(s.uuid) ? DF_CORDON : 0u) |
+                    ((uint32_t)s.mode_id << 3) | ((uint32_t)(s.network_id >= 0 ? s.network_id : 255) << 8);
+      dy.w = (int)df;
+      st.x = s.count; st.y = s.devmem; st.z = s.devcore;
+      st.w = (int)((uint32_t)s.numa | ((uint32_t)s.type_id << 8) | ((uint32_t)s.index << 14) | ((uint32_t)s.vendor_id << 22));
+      h->uuid_index[s.uuid].push_back(((uint32_t)slot << 8) | (uint32_t)d);
+    }
+    h->h_dyn[inv_idx(slot, d)] = dy;
+    h->h_stat[inv_idx(slot, d)] = st;
+  }
+  int16_t* P = h->h_pair.data() + (size_t)slot * 64;
+  for (int i = 0; i < 64; i++) P[i] = 0;
+  for (int i = 0; i < n; i++)
+    for (int j = 0; j < n; j++) {
+      int v = 0;
+      if (node->pair_scores) v = node->pair_scores[(size_t)perm[i] * node->n_devices + perm[j]];
+      if (v > 32767 || v < -32768) { h->err = "pair score outside int16"; return HS_ERR_UNSUPPORTED; }
+      P[i * 8 + j] = (int16_t)v;
+      if (i != j) { if (!have) { have = true; uval = v; } else if (v != uval) uniform = false; }
+    }
+  uint32_t nf = (uint32_t)n | NF_ALIVE | (uniform ? NF_PAIR_UNIFORM : 0u);
+  bool vnpu = h->ascend_vnpu_default;
+  if (ns.vnpu >= 0) vnpu = ns.vnpu == 1;
+  if (vnpu) nf |= NF_VNPU_CORE;
+  h->h_flags[slot] = nf;
+  mark_dirty(h, slot);
+  return HS_OK;
+}
+
+int32_t hs_node_remove(hs_handle* h, const char* name) {
+  if (!h || !name) return HS_ERR_INVALID;
+  auto it = h->node_by_name.find(name);
+  if (it == h->node_by_name.end() || !h->nodes[it->second].alive) return HS_ERR_NOTFOUND;
+  int slot = it->second;
+  NodeSlot& ns = h->nodes[slot];
+  for (size_t d = 0; d < ns.devs.size(); d++) {
+    auto& vec = h->uuid_index[ns.devs[d].uuid];
+    vec.erase(std::remove(vec.begin(), vec.end(), ((uint32_t)slot << 8) | (uint32_t)d), vec.end());
+    if (vec.empty()) h->uuid_index.erase(ns.devs[d].uuid);
+  }
+  ns.alive = false;
+  ns.devs.clear();
+  h->n_alive--;
+  h->has_dead = true;
+  h->h_flags[slot] = 0;
+  for (int d = 0; d < HS_D; d++) { h->h_dyn[inv_idx(slot, d)] = make_int4(0, 0, 0, 0); h->h_stat[inv_idx(slot, d)] = make_int4(0, 0, 0, 0); }
+  mark_dirty(h, slot);
+  return HS_OK;
+}
+
+int32_t hs_usage_apply(hs_handle* h, const char* pod_uid, const char* node, const char* uuid,
+                       int32_t slots, int32_t usedmem, int32_t usedcores) {
+  if (!h || !pod_uid || !node || !uuid) return HS_ERR_INVALID;
+  auto it = h->node_by_name.find(node);
+  if (it == h->node_by_name.end() || !h->nodes[it->second].alive) return HS_ERR_NOTFOUND;
+  int slot = it->second;
+  NodeSlot& ns = h->nodes[slot];
+  auto pit = h->pods.find(pod_uid);
+  if (pit == h->pods.end()) {
+    PodRec pr;
+    pr.node = slot;
+    for (int d = 0; d < HS_D; d++) pr.delta[d] = make_int4(0, 0, 0, 0);
+    pit = h->pods.emplace(pod_uid, pr).first;
+  }
+  if (pit->second.node != slot) { h->err = "pod already holds devices on another node"; return HS_ERR_INVALID; }
+  bool matched = false;
+  for (size_t d = 0; d < ns.devs.size(); d++) {
+    if (ns.devs[d].uuid != uuid) continue;  // scheduler.go:773-785 matches by UUID
+    int4 delta[HS_D];
+    for (int k = 0; k < HS_D; k++) delta[k] = make_int4(0, 0, 0, 0);
+    delta[d] = make_int4(std::max(slots, 1), usedmem, usedcores, 0);
+    apply_host_delta(h, slot, delta, +1);
+    pit->second.delta[d].x += delta[d].x; pit->second.delta[d].y += delta[d].y; pit->second.delta[d].z += delta[d].z;
+    matched = true;
+  }
+  mark_dirty(h, slot);
+  return matched ? HS_OK : HS_ERR_NOTFOUND;
+}
+
+int32_t hs_pod_delete(hs_handle* h, const char* pod_uid) {
+  if (!h || !pod_uid) return HS_ERR_INVALID;
+  auto it = h->pods.find(pod_uid);
+  if (it == h->pods.end()) return HS_ERR_NOTFOUND;
+  apply_host_delta(h, it->second.node, it->second.delta, -1);
+  mark_dirty(h, it->second.node);
+  h->pods.erase(it);
+  return HS_OK;
+}
+
+int32_t hs_rollback(hs_handle* h, const char* pod_uid) { return hs_pod_delete(h, pod_uid); }
+
+int32_t hs_filter(hs_handle* h, const hs_pod* pod, const char* const* node_names, uint32_t n_names,
+                  hs_filter_result* out) {
+  if (!h || !pod || !out) return HS_ERR_INVALID;
+  cudaSetDevice(h->device);
+  h->r_strs.clear();
+  memset(out, 0, sizeof *out);
+  out->node_index = -1;
+  h->have_cand = false;
+  const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
+  if (node_names) {
+    if (!h->b_candpos.ensure(std::max(n_nodes, HS_TILE))) { h->err = "out of memory"; return HS_ERR_CUDA; }
+    for (int i = 0; i < n_nodes; i++) h->b_candpos.h[i] = -1;
+    h->cand_names.clear(); h->cand_slot.clear();
+    for (uint32_t i = 0; i < n_names; i++) {
+      std::string nm = node_names[i] ? node_names[i] : "";
+      auto it = h->node_by_name.find(nm);
+      int s = (it == h->node_by_name.end() || !h->nodes[it->second].alive) ? -1 : it->second;
+      h->cand_names.push_back(nm);
+      h->cand_slot.push_back(s);
+      if (s >= 0) h->b_candpos.h[s] = (int32_t)i;  // a repeated name keeps its last position
+    }
+    h->have_cand = true;
+  }
+  hs_op op;
+  op.kind = HS_OP_FILTER;
+  op.pod = pod;
+  int rc = run_ops(h, &op, 1);
+  if (rc != HS_OK) { out->status = rc; h->have_cand = false; return rc; }
+  if (h->user_status[0] != HS_OK) { out->status = h->user_status[0]; h->have_cand = false; return out->status; }
+  assemble_result(h, h->user_first_op[0], out);
+  h->have_cand = false;
+  return out->status;
+}
+
+int32_t hs_run_batch(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
+  if (!h || (!ops && n_ops)) return HS_ERR_INVALID;
+  cudaSetDevice(h->device);
+  h->have_cand = false;
+  int rc = run_ops(h, ops, n_ops);
+  if (rc != HS_OK) return rc;
+  return (int32_t)n_ops;
+}
+
+int32_t hs_batch_get(hs_handle* h, uint32_t i, hs_filter_result* out) {
+  if (!h || !out || i >= h->user_first_op.size()) return HS_ERR_INVALID;
+  h->r_strs.clear();
+  memset(out, 0, sizeof *out);
+  out->node_index = -1;
+  if (h->user_status[i] != HS_OK) { out->status = h->user_status[i]; return out->status; }
+  if (h->user_first_op[i] < 0) { out->status = HS_ERR_INVALID; return out->status; }
+  assemble_result(h, h->user_first_op[i], out);
+  return out->status;
+}
+
+int32_t hs_snapshot_node(hs_handle* h, const char* node, hs_device_usage_row* rows, uint32_t cap) {
+  if (!h || !node) return HS_ERR_INVALID;
+  auto it = h->node_by_name.find(node);
+  if (it == h->node_by_name.end() || !h->nodes[it->second].alive) return HS_ERR_NOTFOUND;
+  int slot = it->second;
+  // read back from HBM: the device copy is the authority the kernels commit into
+  cudaSetDevice(h->device);
+  if (flush_inventory(h) != HS_OK) return HS_ERR_CUDA;
+  int n = (int)h->nodes[slot].devs.size();
+  for (int d = 0; d < n && (uint32_t)d < cap; d++) {
+    int4 v;
+    if (cudaMemcpy(&v, h->d_dyn + inv_idx(slot, d), sizeof v, cudaMemcpyDeviceToHost) != cudaSuccess) return HS_ERR_CUDA;
+    rows[d].used = v.x; rows[d].usedmem = v.y; rows[d].usedcores = v.z;
+  }
+  return n;
+}
+
+double hs_last_device_ms(const hs_handle* h) { return h ? h->last_ms : 0.0; }
+uint64_t hs_launch_count(const hs_handle* h) { return h ? h->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,463 @@
+// hs_eval.cuh — per-node evaluation of one pod on the device: the integer-level
+// mirror of scoreNode → fitInDevices → <vendor>.Fit → ComputeScore/Less →
+// ComputeDefaultScore/OverrideScore (reference: pkg/scheduler/score.go:81-346,
+// pkg/scheduler/policy/*.go, pkg/device/{nvidia,hygon,cambricon,ascend}/device.go Fit).
+//
+// One thread evaluates one node.  All float math is IEEE binary32 with every
+// operation rounded separately, in the reference's evaluation order (the file
+// is compiled with -fmad=false and uses __fdiv_rn/__fmul_rn/__fadd_rn), so
+// scores and therefore tie-breaks are bit-identical to Go on amd64.
+#pragma once
+#include "hs_types.cuh"
+
+// Working set of one node while a pod is fitted on it.  Arrays are indexed with
+// run-time device slots (sorted order), so they live in local memory / L1.
+struct NodeWork {
+  int used[HS_D], mem[HS_D], cores[HS_D];            // mutable usage copy (NodeUsage.DeepCopy, score.go:320)
+  int count[HS_D], totmem[HS_D], totcore[HS_D];      // capacity
+  uint32_t packed[HS_D], dflags[HS_D];
+  float score[HS_D];                                 // DeviceListsScore.Score
+  uint32_t order;                                    // nibble i = device slot at list position i
+  int ndev;
+};
+
+enum { EV_SCORE = 0, EV_RECORD = 1, EV_EXPLAIN = 2 };
+
+struct EvalOut {
+  // EV_RECORD
+  DevAlloc* allocs;
+  uint32_t n_alloc;
+  // EV_EXPLAIN
+  uint32_t fkind, fcards;
+  uint32_t reasons[16];
+};
+
+__device__ __forceinline__ int ord_get(uint32_t order, int i) { return (order >> (4 * i)) & 7; }
+__device__ __forceinline__ uint32_t ord_swap(uint32_t order, int i, int j) {
+  uint32_t a = (order >> (4 * i)) & 15u, b = (order >> (4 * j)) & 15u;
+  order &= ~((15u << (4 * i)) | (15u << (4 * j)));
+  return order | (b << (4 * i)) | (a << (4 * j));
+}
+
+// DeviceListsScore.ComputeScore, policy/gpu_policy.go:194-222
+__device__ __forceinline__ float dev_compute_score(const NodeWork& w, int d, const DevPod& pod, const DevEntry* ent, int eb, int ee) {
+  if (w.count[d] == 0 || w.totcore[d] == 0 || w.totmem[d] == 0) return 0.0f;
+  int request = 0, core = 0, mem = 0;
+  const uint64_t tbit = 1ull << PK_TYPE(w.packed[d]);
+  for (int e = eb; e < ee; e++) {
+    if (!(ent[e].type_equal & tbit)) continue;
+    request += 1;
+    core += ent[e].coresreq;
+    if (ent[e].mempct != 0 && ent[e].mempct != 101) {
+      mem += (int)(((long long)w.totmem[d] * (long long)ent[e].mempct) / 100);
+      continue;
+    }
+    mem += ent[e].memreq;
+  }
+  float usedScore = __fdiv_rn((float)(request + w.used[d]), (float)w.count[d]);
+  float coreScore = __fdiv_rn((float)(core + w.cores[d]), (float)w.totcore[d]);
+  float memScore = __fdiv_rn((float)(mem + w.mem[d]), (float)w.totmem[d]);
+  float s = __fadd_rn(__fmul_rn(pod.w_slot, usedScore), __fmul_rn(pod.w_core, coreScore));
+  s = __fadd_rn(s, __fmul_rn(pod.w_mem, memScore));
+  return __fmul_rn(10.0f, s);
+}
+
+// DeviceUsageList.Less, policy/gpu_policy.go:77-167 (a, b are device slots)
+__device__ __forceinline__ bool dev_less(const NodeWork& w, const DevPod& pod, int a, int b) {
+  const float si = w.score[a], sj = w.score[b];
+  const int ni = PK_NUMA(w.packed[a]), nj = PK_NUMA(w.packed[b]);
+  switch (pod.sort_mode) {
+    case SORT_CHAIN: {
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const int key = pod.chain[k];
+        if (key == CK_BINPACK) { if (si != sj) return si < sj; }
+        else if (key == CK_SPREAD) { if (si != sj) return si > sj; }
+        else if (key == CK_NUMA) { if (ni != nj) return ni < nj; }
+      }
+      return PK_INDEX(w.packed[a]) < PK_INDEX(w.packed[b]);
+    }
+    case SORT_MUTEX: {
+      const int ui = w.used[a], uj = w.used[b];
+      if (ui != uj) return ui > uj;
+      return ni < nj;
+    }
+    case SORT_NUMA_BINPACK:
+      if (ni == nj) return si < sj;
+      return ni > nj;
+    case SORT_NUMA_SPREAD:
+      if (ni == nj) return si > sj;
+      return ni < nj;
+    case SORT_BINPACK:
+      if (si != sj) return si < sj;
+      return ni < nj;
+    default:  // SORT_SPREAD
+      if (si != sj) return si > sj;
+      return ni < nj;
+  }
+}
+
+// sort.Sort for n <= 12 == stable insertion sort (Go stdlib pdqsort, maxInsertion 12)
+__device__ __forceinline__ void dev_sort(NodeWork& w, const DevPod& pod) {
+  uint32_t order = w.order;
+  for (int i = 1; i < w.ndev; i++) {
+    for (int j = i; j > 0 && dev_less(w, pod, ord_get(order, j), ord_get(order, j - 1)); j--)
+      order = ord_swap(order, j, j - 1);
+  }
+  w.order = order;
+}
+
+// NodeScore.ComputeDefaultScore, policy/node_policy.go:106-130
+__device__ __forceinline__ float node_default_score(const NodeWork& w) {
+  int used = 0, usedCore = 0, usedMem = 0, total = 0, totalCore = 0, totalMem = 0;
+  for (int d = 0; d < w.ndev; d++) {
+    used += w.used[d]; usedCore += w.cores[d]; usedMem += w.mem[d];
+    total += w.count[d]; totalCore += w.totcore[d]; totalMem += w.totmem[d];
+  }
+  if (total == 0 || totalCore == 0 || totalMem == 0) return 0.0f;
+  float useScore = __fdiv_rn((float)used, (float)total);
+  float coreScore = __fdiv_rn((float)usedCore, (float)totalCore);
+  float memScore = __fdiv_rn((float)usedMem, (float)totalMem);
+  return __fmul_rn(10.0f, __fadd_rn(__fadd_rn(useScore, coreScore), memScore));
+}
+
+// use/no-use UUID lists resolved by the host into sorted (node<<8 | mask) words
+__device__ __forceinline__ uint32_t uuid_mask_lookup(const uint32_t* pool, uint32_t off, uint32_t cnt, uint32_t node) {
+  uint32_t lo = 0, hi = cnt;
+  while (lo < hi) {
+    uint32_t mid = (lo + hi) >> 1;
+    uint32_t v = pool[off + mid];
+    if ((v >> 8) < node) lo = mid + 1; else hi = mid;
+  }
+  if (lo < cnt) {
+    uint32_t v = pool[off + lo];
+    if ((v >> 8) == node) return v & 255u;
+  }
+  return 0;
+}
+
+struct FitCtx {
+  int tmp_dev[HS_D];    // tmpDevs[k.Type]: device slots in pick order
+  int tmp_mem[HS_D];    // their resolved memreq
+  int ntmp;
+  int cores;            // k.Coresreq after the 100 clamp
+};
+
+#define REASON(r) do { if (MODE == EV_EXPLAIN) out.reasons[r]++; } while (0)
+
+// <vendor>.Fit: nvidia/device.go:715-876, hygon/device.go:264-369, cambricon/device.go:378-488,
+// ascend/device.go:442-617 — one backward scan with per-vendor gates.
+// td[0..cnt) = typeDevices (device slots, sorted list order).  Returns fit; the picks are in fc.
+template <int MODE>
+__device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e, const int* td, int cnt,
+                        uint32_t node, uint32_t nflags, const KernelArgs& ka, FitCtx& fc, EvalOut& out) {
+  const int vendor = e.vendor;
+  const bool isNv = vendor == HV_NVIDIA;
+  const bool isAscend = vendor >= HV_ASCEND0;
+  int k_nums = e.nums;
+  const int origin = e.nums;
+  int prevnuma = -1;
+  fc.ntmp = 0;
+  fc.cores = e.coresreq > 100 ? 100 : e.coresreq;
+  const bool isMutex = pod.flags & PF_MUTEX;
+  bool needTopology = isNv && (pod.flags & PF_TOPOLOGY);
+  const bool isHAMiCore = isAscend && (pod.flags & PF_ASCEND_HAMICORE);
+  if (MODE == EV_EXPLAIN) {
+    for (int r = 0; r < 16; r++) out.reasons[r] = 0;
+    out.fkind = FK_HIST;
+    out.fcards = (uint32_t)cnt;
+  }
+  if (isAscend) {
+    if (isHAMiCore && !(nflags & NF_VNPU_CORE)) {  // ascend/device.go:469-473
+      REASON(14 /*ModeNotFit*/);
+      return false;
+    }
+    if (e.flags & EF_ASCEND910) {                  // hasNetworkID, ascend/device.go:476-480
+      bool all = true;
+      for (int i = 0; i < cnt; i++) if (DF_NET(w.dflags[td[i]]) == 255u) { all = false; break; }
+      if (all) needTopology = true;
+    }
+  }
+  const bool is910CMulti = isAscend && (e.flags & EF_ASCEND910C) && origin > 1;
+  const bool decrement = isNv ? !needTopology : (isAscend ? (!needTopology && !is910CMulti) : true);
+  uint32_t useMask = 0xffu, nouseMask = 0u;
+  if (e.has_use) useMask = uuid_mask_lookup(ka.uuid_pool, e.use_off, e.use_cnt, node);
+  if (e.nouse_cnt) nouseMask = uuid_mask_lookup(ka.uuid_pool, e.nouse_off, e.nouse_cnt, node);
+  const bool numaAssert = isNv && (pod.flags & PF_NUMA_ASSERT);
+
+  for (int i = cnt - 1; i >= 0; i--) {
+    const int d = td[i];
+    const uint32_t df = w.dflags[d];
+    const uint32_t pk = w.packed[d];
+    if (!(df & DF_HEALTH)) { REASON(6); continue; }
+    if (isNv && (df & DF_CORDON)) { REASON(7); continue; }
+    bool found = (e.type_allow >> PK_TYPE(pk)) & 1ull;
+    if (isNv && !((e.mode_allow >> DF_MODE(df)) & 1u)) found = false;
+    if (!found) { REASON(0); continue; }
+    const int numa = PK_NUMA(pk);
+    if (numaAssert && prevnuma != numa) {
+      if (k_nums != origin) { if (MODE == EV_EXPLAIN) out.reasons[8] += (uint32_t)fc.ntmp; }
+      k_nums = origin;
+      prevnuma = numa;
+      fc.ntmp = 0;
+    }
+    if (!((useMask >> d) & 1u) || ((nouseMask >> d) & 1u)) { REASON(1); continue; }
+    if (w.count[d] <= w.used[d]) { REASON(2); continue; }
+    if (isMutex && w.used[d] > 0) { REASON(9); continue; }
+    int memreq = 0;
+    if (e.memreq > 0) memreq = e.memreq;
+    if (e.mempct != 101 && e.memreq == 0) memreq = (int)((unsigned)w.totmem[d] * (unsigned)e.mempct) / 100;
+    if (w.totmem[d] - w.mem[d] < memreq) { REASON(4); continue; }
+    const int etc = isHAMiCore ? 100 : w.totcore[d];
+    if (etc - w.cores[d] < fc.cores) { REASON(5); continue; }
+    if (etc == 100 && fc.cores == 100 && w.used[d] > 0) { REASON(9); continue; }
+    if (etc != 0 && w.cores[d] == etc && fc.cores == 0) { REASON(3); continue; }
+    if (k_nums > 0) {
+      if (decrement) k_nums--;
+      fc.tmp_dev[fc.ntmp] = d;
+      fc.tmp_mem[fc.ntmp] = memreq;
+      fc.ntmp++;
+    }
+    if (k_nums == 0 && decrement) return true;
+  }
+
+  if (is910CMulti) {
+    // computeBestCombination910C, ascend/device.go:677-733 (equal-size cards in ascending card id)
+    int sel_dev[HS_D], sel_mem[HS_D], nsel = 0;
+    int task = origin;
+    // indexToDevice is keyed by Idx: a later candidate with the same Idx replaces an earlier one
+    for (int pass = 0; pass < 1; pass++) {
+      // full cards (both NPUs present among the candidates), ascending card id
+      for (int card = 0; card < 128 && task > 0; card++) {
+        int members[HS_D], nm = 0;
+        for (int t = 0; t < fc.ntmp; t++)
+          if (PK_INDEX(w.packed[fc.tmp_dev[t]]) / 2 == card) members[nm++] = t;
+        if (nm == 0) continue;
+        if (nm == 2) {
+          for (int m = 0; m < nm && nsel < HS_D; m++) {
+            // map the index back through indexToDevice (last candidate with that Idx wins)
+            const int idx = PK_INDEX(w.packed[fc.tmp_dev[members[m]]]);
+            int pick = members[m];
+            for (int t = 0; t < fc.ntmp; t++) if (PK_INDEX(w.packed[fc.tmp_dev[t]]) == idx) pick = t;
+            sel_dev[nsel] = fc.tmp_dev[pick];
+            sel_mem[nsel] = fc.tmp_mem[pick];
+            nsel++;
+          }
+          task -= 2;
+        }
+      }
+    }
+    if (nsel != origin) {
+      if (MODE == EV_EXPLAIN) { out.reasons[12] = (uint32_t)nsel; out.fcards = (uint32_t)origin; }
+      return false;
+    }
+    for (int t = 0; t < nsel; t++) { fc.tmp_dev[t] = sel_dev[t]; fc.tmp_mem[t] = sel_mem[t]; }
+    fc.ntmp = nsel;
+    return true;
+  }
+
+  if (needTopology) {
+    if (fc.ntmp == origin) return true;
+    if (fc.ntmp > origin) {
+      const int m = fc.ntmp;
+      if (isNv) {
+        const bool uniform = nflags & NF_PAIR_UNIFORM;
+        const int16_t* P = ka.pair + (size_t)node * 64;
+        if (origin == 1) {
+          // computeWorstSingleCard, nvidia/device.go:927-951: first strictly-lowest Σ pair score
+          int best = 0;
+          if (!uniform) {
+            int worst = 0;
+            bool have = false;
+            for (int a = 0; a < m; a++) {
+              int total = 0;
+              for (int b = 0; b < m; b++) if (b != a) total += (int)P[fc.tmp_dev[a] * 8 + fc.tmp_dev[b]];
+              if (!have || total < worst) { have = true; worst = total; best = a; }
+            }
+          }
+          fc.tmp_dev[0] = fc.tmp_dev[best];
+          fc.tmp_mem[0] = fc.tmp_mem[best];
+          fc.ntmp = 1;
+          return true;
+        }
+        // generateCombinations + computeBestCombination, nvidia/device.go:887-915,953-978:
+        // lexicographic enumeration, first strictly-highest Σ pairwise score wins.
+        uint32_t bestMask = (1u << origin) - 1u;  // the first combination
+        if (!uniform) {
+          int bestScore = 0;
+          bool have = false;
+          for (uint32_t mask = 1; mask < (1u << m); mask++) {
+            if (__popc(mask) != origin) continue;
+            int total = 0;
+            for (int a = 0; a < m; a++) {
+              if (!((mask >> a) & 1u)) continue;
+              for (int b = a + 1; b < m; b++)
+                if ((mask >> b) & 1u) total += (int)P[fc.tmp_dev[a] * 8 + fc.tmp_dev[b]];
+            }
+            bool take;
+            if (!have) take = true;
+            else if (total != bestScore) take = total > bestScore;
+            else {  // equal score: the lexicographically earlier combination was enumerated first
+              const uint32_t diff = mask ^ bestMask;
+              take = (mask & (diff & (0u - diff))) != 0;
+            }
+            if (take) { have = true; bestScore = total; bestMask = mask; }
+          }
+        }
+        int n = 0;
+        for (int a = 0; a < m; a++)
+          if ((bestMask >> a) & 1u) { fc.tmp_dev[n] = fc.tmp_dev[a]; fc.tmp_mem[n] = fc.tmp_mem[a]; n++; }
+        fc.ntmp = n;
+        return true;
+      }
+      // Ascend NetworkID topology, ascend/device.go:599-607,631-675
+      if (origin == 1) { fc.ntmp = 1; return true; }
+      int sel_dev[HS_D], sel_mem[HS_D], nsel = 0;
+      uint32_t taken = 0;  // candidates already emitted
+      while (nsel < origin) {
+        // next group: largest remaining count, ties → ascending NetworkID (canonical rule 7)
+        int bestNet = -1, bestCnt = 0;
+        for (int a = 0; a < m; a++) {
+          if ((taken >> a) & 1u) continue;
+          const int net = (int)DF_NET(w.dflags[fc.tmp_dev[a]]);
+          int c = 0;
+          for (int b = 0; b < m; b++)
+            if (!((taken >> b) & 1u) && (int)DF_NET(w.dflags[fc.tmp_dev[b]]) == net) c++;
+          if (c > bestCnt || (c == bestCnt && net < bestNet)) { bestCnt = c; bestNet = net; }
+        }
+        if (bestNet < 0) break;
+        for (int a = 0; a < m && nsel < origin; a++) {
+          if ((taken >> a) & 1u) continue;
+          if ((int)DF_NET(w.dflags[fc.tmp_dev[a]]) != bestNet) continue;
+          sel_dev[nsel] = fc.tmp_dev[a];
+          sel_mem[nsel] = fc.tmp_mem[a];
+          nsel++;
+        }
+        for (int a = 0; a < m; a++)
+          if ((int)DF_NET(w.dflags[fc.tmp_dev[a]]) == bestNet) taken |= 1u << a;
+      }
+      for (int t = 0; t < nsel; t++) { fc.tmp_dev[t] = sel_dev[t]; fc.tmp_mem[t] = sel_mem[t]; }
+      fc.ntmp = nsel;
+      return true;
+    }
+  }
+  if (fc.ntmp > 0) { if (MODE == EV_EXPLAIN) out.reasons[12] = (uint32_t)fc.ntmp; }
+  return false;
+}
+
+// fitInDevices, score.go:81-137, for the entries [eb, ee) of one container
+template <int MODE>
+__device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry* ent, int eb, int ee,
+                                  uint32_t node, uint32_t nflags, const KernelArgs& ka, EvalOut& out,
+                                  float* score_acc, uint32_t* score_zero) {
+  for (int d = 0; d < w.ndev; d++) w.score[d] = dev_compute_score(w, d, pod, ent, eb, ee);
+  for (int ei = eb; ei < ee; ei++) {
+    const DevEntry& e = ent[ei];
+    dev_sort(w, pod);
+    if (e.vendor == HV_NONE) {
+      if (MODE == EV_EXPLAIN) out.fkind = FK_TYPE_NOT_FOUND;
+      return false;
+    }
+    int td[HS_D], cnt = 0;
+    bool anyMig = false;
+    for (int i = 0; i < w.ndev; i++) {
+      const int d = ord_get(w.order, i);
+      if ((e.type_contains >> PK_TYPE(w.packed[d])) & 1ull) {
+        td[cnt++] = d;
+        if (DF_MODE(w.dflags[d]) == 2u) anyMig = true;
+      }
+    }
+    // isMIGRequest, score.go:54-69 (MIG devices are refused at upsert, so anyMig is false)
+    const bool migReq = e.vendor == HV_NVIDIA && (e.flags & EF_MIGMODE_OK) && anyMig;
+    if (e.nums > cnt && !migReq) {
+      if (MODE == EV_EXPLAIN) out.fkind = FK_NODE_INSUFFICIENT;
+      return false;
+    }
+    FitCtx fc;
+    if (!dev_fit<MODE>(w, pod, e, td, cnt, node, nflags, ka, fc, out)) return false;
+    // AddResourceUsage per pick (nvidia/device.go:645-664 non-MIG; identical for the other vendors)
+    int netcnt_max = 0;
+    bool missing_net = false;
+    for (int t = 0; t < fc.ntmp; t++) {
+      const int d = fc.tmp_dev[t];
+      w.used[d] += 1;
+      w.cores[d] += fc.cores;
+      w.mem[d] += fc.tmp_mem[t];
+      if (MODE == EV_RECORD && out.n_alloc < HS_MAX_ALLOC) {
+        DevAlloc a;
+        a.entry = (uint8_t)(ei);
+        a.dev = (uint8_t)d;
+        a.usedcores = (int16_t)fc.cores;
+        a.usedmem = fc.tmp_mem[t];
+        out.allocs[out.n_alloc++] = a;
+      }
+      if (e.score_slot >= 0) {
+        const int net = (int)DF_NET(w.dflags[d]);
+        if (net == 255) missing_net = true;
+        int c = 0;
+        for (int u = 0; u < fc.ntmp; u++) if ((int)DF_NET(w.dflags[fc.tmp_dev[u]]) == net) c++;
+        if (c > netcnt_max) netcnt_max = c;
+      }
+    }
+    // Ascend ScoreNode per container, ascend/device.go:388-424
+    if (e.score_slot >= 0 && fc.ntmp > 0) {
+      if (missing_net) *score_zero |= 1u << e.score_slot;
+      else score_acc[e.score_slot] = __fadd_rn(score_acc[e.score_slot], __fdiv_rn((float)netcnt_max, (float)fc.ntmp));
+    }
+  }
+  return true;
+}
+
+// scoreNode, score.go:294-346.  `base` usage must already be in w.used/mem/cores.
+// Returns fit; *score_out = node score (pre-allocation default score + vendor ScoreNode terms).
+template <int MODE>
+__device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* ent, uint32_t node, uint32_t nflags,
+                               const KernelArgs& ka, EvalOut& out, float* score_out) {
+  float score_acc[HS_SCORE_SLOTS];
+  uint32_t score_zero = 0;
+#pragma unroll
+  for (int s = 0; s < HS_SCORE_SLOTS; s++) score_acc[s] = 0.0f;
+  const uint32_t identity = 0x76543210u;
+  const float pre = node_default_score(w);  // on the pre-allocation usage (score.go:320-328)
+
+  if (pod.n_init > 0) {
+    int bu[HS_D], bm[HS_D], bc[HS_D];
+    for (int d = 0; d < w.ndev; d++) { bu[d] = w.used[d]; bm[d] = w.mem[d]; bc[d] = w.cores[d]; }
+    for (int c = 0; c < pod.n_init && c < pod.n_ctr; c++) {
+      const int eb = pod.ctr_begin[c], ee = pod.ctr_begin[c + 1];
+      if (eb == ee) continue;  // len(req) == 0: padded on the host
+      w.order = identity;      // node.DeepCopy(): registration order, fresh usage (score.go:241)
+      if (!dev_fit_container<MODE>(w, pod, ent, eb, ee, node, nflags, ka, out, score_acc, &score_zero)) return false;
+      for (int d = 0; d < w.ndev; d++) { w.used[d] = bu[d]; w.mem[d] = bm[d]; w.cores[d] = bc[d]; }
+    }
+  }
+  w.order = identity;
+  for (int c = pod.n_init; c < pod.n_ctr; c++) {
+    const int eb = pod.ctr_begin[c], ee = pod.ctr_begin[c + 1];
+    int sums = 0;
+    for (int e = eb; e < ee; e++) sums += ent[e].nums;
+    if (sums == 0) continue;
+    if (!dev_fit_container<MODE>(w, pod, ent, eb, ee, node, nflags, ka, out, score_acc, &score_zero)) return false;
+  }
+  // OverrideScore, policy/node_policy.go:67-95: Σ vendor ScoreNode in sorted type-key order
+  float devScore = 0.0f;
+#pragma unroll
+  for (int s = 0; s < HS_SCORE_SLOTS; s++) {
+    const float v = ((score_zero >> s) & 1u) ? 0.0f : __fmul_rn(score_acc[s], 10.0f);
+    devScore = __fadd_rn(devScore, v);
+  }
+  *score_out = __fadd_rn(pre, devScore);
+  return true;
+}
+
+// Order-preserving key: best node == max key.  hi 32 bits: float32 score mapped to
+// an unsigned that sorts like the float (inverted for node policy "spread", which picks
+// the MIN score, node_policy.go:48-54); lo 32 bits: candidate position + 1, so among
+// equal scores the highest position wins (canonical rule 3) and 0 means "no node".
+__device__ __forceinline__ unsigned long long make_key(float score, bool spread, uint32_t pos) {
+  if (score == 0.0f) score = 0.0f;  // -0 == +0 in Go's comparison
+  uint32_t u = __float_as_uint(score);
+  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  if (spread) u = ~u;
+  return ((unsigned long long)u << 32) | (unsigned long long)(pos + 1u);
+}

@@ -1,0 +1,147 @@
+// hs_types.cuh — plain structs shared by the host side (hs_engine.cu) and the
+// sm_100a kernels (hs_kernels.cu).  Everything the device sees is integers:
+// strings (types, UUIDs, policies, annotations) are resolved on the host.
+#pragma once
+#include <stdint.h>
+
+#define HS_D 8            // device slots per node
+#define HS_TILE 32        // nodes per inventory tile (one warp wide)
+#define HS_MAX_E 16       // (container, vendor) request entries per pod
+#define HS_MAX_C 16       // containers per pod
+#define HS_MAX_ALLOC 64   // allocation rows one decision can produce
+#define HS_SCORE_SLOTS 4  // distinct Ascend910* type keys per pod that contribute ScoreNode
+
+// ---- inventory in HBM -------------------------------------------------------
+// Structure-of-arrays in tiles of 32 nodes: for tile t, device slot d, lane n
+//   dyn [ (t*HS_D + d)*HS_TILE + n ]  = {used, usedmem, usedcores, dflags}
+//   stat[ (t*HS_D + d)*HS_TILE + n ]  = {count, totalmem, totalcore, packed}
+// so a warp that owns one tile reads each (d) row as one coalesced 512 B line
+// group with 128-bit loads.  32 B per device, 256 B per node.
+//
+// dflags: bit0 health | bit1 cordoned | bit2 present | bits3-5 mode id | bits8-15 NetworkID (255 = none)
+// packed: bits0-7 numa | bits8-13 type id | bits14-21 DeviceInfo.Index | bits22-25 vendor id
+#define DF_HEALTH 1u
+#define DF_CORDON 2u
+#define DF_PRESENT 4u
+#define DF_MODE(x) (((x) >> 3) & 7u)
+#define DF_NET(x) (((x) >> 8) & 255u)
+#define PK_NUMA(x) ((int)((x) & 255u))
+#define PK_TYPE(x) (((x) >> 8) & 63u)
+#define PK_INDEX(x) ((int)(((x) >> 14) & 255u))
+#define PK_VENDOR(x) (((x) >> 22) & 15u)
+
+// node_flags: bits0-3 ndev | bit4 alive | bit5 pair scores uniform | bit6 hami-vnpu-core supported
+#define NF_NDEV(x) ((int)((x) & 15u))
+#define NF_ALIVE 16u
+#define NF_PAIR_UNIFORM 32u
+#define NF_VNPU_CORE 64u
+
+// vendor predicate ids (device-side switch, one code path, no dispatch layer)
+enum { HV_NVIDIA = 0, HV_DCU = 1, HV_MLU = 2, HV_ASCEND0 = 3, HV_NONE = 15 };
+
+// GPU-policy comparator (policy/gpu_policy.go:77-167), resolved on the host
+enum { SORT_BINPACK = 0, SORT_SPREAD = 1, SORT_MUTEX = 2, SORT_NUMA_BINPACK = 3, SORT_NUMA_SPREAD = 4, SORT_CHAIN = 5 };
+enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
+
+// entry flags
+#define EF_ASCEND910 1u     // CommonWord has prefix "Ascend910": NetworkID topology + ScoreNode
+#define EF_ASCEND910C 2u    // k.Type == "Ascend910C": module pairing
+#define EF_MIGMODE_OK 4u    // pod's vgpu-mode annotation is absent or contains "mig" (isMIGRequest)
+
+struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 64 B
+  int32_t nums, memreq, mempct, coresreq;
+  uint64_t type_contains;   // bit t: lower(type t) contains lower(k.Type)          (score.go:43-52)
+  uint64_t type_equal;      // bit t: k.Type == type t exactly                     (gpu_policy.go:203)
+  uint64_t type_allow;      // bit t: checkType verdict for type t                 (devices.go:719-738)
+  uint32_t mode_allow;      // bit m: nvidia.com/vgpu-mode contains mode m         (nvidia/device.go:495-498)
+  uint16_t vendor;          // HV_*; HV_NONE → "Device type not found"
+  uint16_t flags;
+  uint32_t use_off, use_cnt;     // sorted (node<<8 | mask8) words in the uuid pool: use-uuid list
+  uint32_t nouse_off, nouse_cnt; // same for the no-use list
+  int8_t score_slot;        // ScoreNode accumulator (Ascend910*), -1 none
+  uint8_t has_use;          // a non-empty use-uuid annotation exists
+  uint8_t key_id;           // id of k.Type among the pod's distinct type keys (PodDevices key)
+  uint8_t is_init;          // entry belongs to an init container
+  uint32_t pad2;
+};
+
+// pod flags
+#define PF_NODE_SPREAD 1u   // node policy == "spread": pick the MIN score (node_policy.go:48-54)
+#define PF_MUTEX 2u         // PolicyContains(gpuPolicy, "mutex")
+#define PF_TOPOLOGY 4u      // PolicyContains(gpuPolicy, "topology-aware")  (NVIDIA)
+#define PF_NUMA_ASSERT 8u   // nvidia.com/numa-bind parses true (assertNuma)
+#define PF_ASCEND_HAMICORE 16u // huawei.com/vnpu-mode == "hami-core"
+
+enum { OP_FILTER = 0, OP_RELEASE = 1, OP_NOP = 2 };
+
+struct DevPod {             // one op of the stream, 96 B + entries
+  uint32_t op;              // OP_*
+  uint32_t flags;           // PF_*
+  uint8_t sort_mode;        // SORT_*
+  uint8_t chain[3];         // CK_* keys in order (SORT_CHAIN)
+  uint8_t n_ctr, n_init, n_entries, pad;
+  float w_slot, w_core, w_mem;   // float32(int64 weight)
+  uint32_t entry_off;       // first DevEntry in the entry pool
+  uint8_t ctr_begin[HS_MAX_C + 1]; // container c owns entries [ctr_begin[c], ctr_begin[c+1])
+  uint8_t pad3[3];
+  // OP_RELEASE: subtract a committed allocation.
+  int32_t rel_node;         // node slot, or -1 = take node and deltas from decision `rel_ref` of this batch
+  int32_t rel_ref;
+  int32_t rel_off;          // first of HS_D {slots, mem, cores, 0} int4 rows in the release pool
+  uint32_t pad4[4];
+};
+
+struct DevAlloc {           // one ContainerDevice, 8 B
+  uint8_t entry;            // index into the pod's entries (container + type)
+  uint8_t dev;              // device slot on the node
+  int16_t usedcores;
+  int32_t usedmem;
+};
+
+struct DevDecision {        // 16 B header; rows live in the alloc pool
+  int32_t status;           // 0 fit, 1 no fit, 2 release/nop done, <0 error
+  int32_t node;             // node slot
+  float score;
+  uint32_t alloc_off;       // first DevAlloc
+  uint32_t n_alloc;
+  uint32_t fail_slot;       // no fit: slot in the fail buffer holding the per-node reasons (0xFFFFFFFF = not recorded)
+  uint32_t pad[2];
+};
+
+// per-node failure record written only when a decision finds no node (common.go:46-53)
+enum { FK_NONE = 0, FK_HIST = 1, FK_NODE_INSUFFICIENT = 2, FK_TYPE_NOT_FOUND = 3, FK_NOT_CANDIDATE = 4 };
+struct DevFail {            // 16 B
+  uint32_t kind_cards;      // bits0-3 kind | bits4-31 cards denominator
+  uint32_t c0;              // reasons 0-7, 4 bits each (HS_R_* order)
+  uint32_t c1;              // reasons 8-14
+  uint32_t pad;
+};
+
+struct KernelArgs {
+  // inventory
+  int4* dyn;
+  const int4* stat;
+  const uint32_t* node_flags;
+  const int16_t* pair;          // [node][64]
+  int32_t n_nodes;              // slots (padded to HS_TILE)
+  // candidate positions: NULL = every alive node, position == slot
+  const int32_t* cand_pos;      // per slot: position in NodeNames or -1
+  // ops
+  const DevPod* pods;
+  const DevEntry* entries;
+  const uint32_t* uuid_pool;
+  const int4* rel_pool;
+  int32_t n_ops;                // ops [op_begin, n_ops) run in this launch
+  int32_t op_begin;
+  // results
+  DevDecision* decisions;
+  DevAlloc* allocs;
+  uint32_t alloc_cap;
+  int4* commit_delta;           // [op][HS_D] collapsed {slots, mem, cores, 0} of a committed decision
+  unsigned long long* best;     // [op] packed argbest key, zeroed by the host
+  DevFail* fail;                // [fail_cap][n_nodes]
+  uint32_t fail_cap;
+  uint32_t* counters;           // [0] alloc cursor, [1] fail cursor, [2] ops completed, [3] barrier arrive, [4] barrier epoch
+  // multi-GPU: global position of this shard's slot 0 (argbest key carries global positions)
+  int32_t pos_base;
+};

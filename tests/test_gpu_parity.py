@@ -1,0 +1,138 @@
+"""Parity tests proper: the CUDA engine, called through the C ABI, against the CPU oracle
+on the same seeded inputs.  Bar: bit-exact (node, device UUIDs, memreq/cores, float32 score
+bits, annotation strings, FailedNodes reason strings, final usage cache)."""
+import json
+import os
+
+import pytest
+
+import parity
+from oracle_abi import abi
+
+pytestmark = pytest.mark.gpu
+
+
+def _gen():
+    import k8s_vgpu_scheduler_b200.gen as gen
+    return gen
+
+
+def _check(cfg, nodes, ops, **kw):
+    ref, rsnap = parity.run_oracle(cfg, nodes, ops)
+    got, gsnap = parity.run_engine(cfg, nodes, ops, **kw)
+    bad = parity.compare(ops, ref, got, rsnap, gsnap)
+    assert not bad, "\n".join(bad)
+    return ref
+
+
+def test_c1_saturating_binpack():
+    # BASELINE config 1 at full size: 96 fits then 904 no-fits with FailedNodes reasons (F10)
+    cfg, nodes, ops = _gen().config1()
+    ref = _check(cfg, nodes, ops)
+    fits = sum(1 for r in ref if r["status"] == abi.HS_FIT)
+    assert fits == 96 and len(ref) == 1000
+
+
+def test_c1_with_departures():
+    cfg, nodes, ops = _gen().config1(n_pods=600, departures=0.3)
+    _check(cfg, nodes, ops)
+
+
+def test_c1_single_calls_match_batch():
+    cfg, nodes, ops = _gen().config1(n_pods=150, departures=0.3)
+    _check(cfg, nodes, ops, batch=False)
+
+
+def test_c2_mixed_spread():
+    cfg, nodes, ops = _gen().config2(n_nodes=200, n_pods=3000)
+    _check(cfg, nodes, ops)
+
+
+def test_c3_topology_numa():
+    cfg, nodes, ops = _gen().config3(n_nodes=300, n_pods=2000)
+    _check(cfg, nodes, ops)
+
+
+def test_c4_heterogeneous_selectors():
+    cfg, nodes, ops = _gen().config4(n_nodes=400, n_pods=4000)
+    _check(cfg, nodes, ops)
+
+
+def test_mixed_features():
+    cfg, nodes, ops = _gen().mixed_features()
+    _check(cfg, nodes, ops)
+
+
+def test_chunked_batches_and_fail_buffer_resume():
+    # many no-fit decisions in one batch overflow the device fail buffer: the kernel stops, the host drains and resumes
+    cfg, nodes, ops = _gen().config1(n_pods=300)
+    _check(cfg, nodes, ops, chunk=97)
+
+
+def test_streaming_mode_many_nodes():
+    # more nodes than resident threads: every decision re-reads the SoA inventory from HBM/L2
+    cfg, nodes, ops = _gen().config2(n_nodes=40000, n_pods=300)
+    _check(cfg, nodes, ops)
+
+
+def test_candidate_list_and_unregistered():
+    import k8s_vgpu_scheduler_b200.engine as eng
+    import oracle_abi as oa
+    cfg, nodes, ops = _gen().config2(n_nodes=64, n_pods=40)
+    o = oa.Oracle(cfg["node_policy"], cfg["gpu_policy"])
+    e = eng.Engine(cfg["node_policy"], cfg["gpu_policy"])
+    for n in nodes:
+        o.node_upsert(n)
+        e.node_upsert(n)
+    names = [n["name"] for n in nodes]
+    cand = [names[5], "ghost-node", names[3], names[40], names[17]]
+    for kind, arg in ops:
+        if kind != "filter":
+            continue
+        r, g = o.filter(arg, cand), e.filter(arg, cand)
+        bad = parity.compare([("filter", arg)], [r], [g])
+        assert not bad, "\n".join(bad)
+    # a pod nothing can hold: FailedNodes carries every candidate incl. the unregistered one
+    big = {"uid": "big", "containers": [[{"type": "NVIDIA", "nums": 9, "memreq": 1, "mempct": 101, "coresreq": 0}]]}
+    r, g = o.filter(big, cand), e.filter(big, cand)
+    assert r["status"] == g["status"] == abi.HS_NOFIT
+    assert r["failed"] == g["failed"] and g["failed"]["ghost-node"] == "node unregistered"
+    o.close()
+    e.close()
+
+
+def test_golden_filter_cases_on_gpu():
+    # the reference's own Test_Filter fixture (scheduler_test.go:509-943) through the CUDA engine
+    import k8s_vgpu_scheduler_b200.engine as eng
+    g = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    M = json.load(open(os.path.join(g, "manual.json")))["filter"]
+    cases = json.load(open(os.path.join(g, "filter.json")))["cases"]
+    for case in cases:
+        e = eng.Engine()
+        for n in M["nodes"]:
+            e.node_upsert(n)
+        for uid, node, uuid, mem, cores in M["pods"]:
+            assert e.usage_apply(uid, node, uuid, 0, mem, cores) == 0
+        podj = case["args"]["Pod"]
+        spec = podj["Spec"]
+        ctrs = []
+        for c in (spec.get("InitContainers") or []) + (spec.get("Containers") or []):
+            lim = ((c.get("Resources") or {}).get("Limits")) or {}
+            if "hami.io/gpu" not in lim:
+                ctrs.append([])
+                continue
+            mem = int(lim.get("hami.io/gpumem", 0))
+            pct = int(lim.get("hami.io/gpumem-percentage", 101))
+            if pct == 101 and mem == 0:
+                pct = 100
+            ctrs.append([{"key": "NVIDIA", "type": "NVIDIA", "nums": int(lim["hami.io/gpu"]), "memreq": mem,
+                          "mempct": pct, "coresreq": int(lim.get("hami.io/gpucores", 0))}])
+        pod = {"uid": podj["ObjectMeta"].get("UID", "u"), "annotations": podj["ObjectMeta"].get("Annotations") or {},
+               "containers": ctrs, "n_init": len(spec.get("InitContainers") or [])}
+        out = e.filter(pod, case["args"]["NodeNames"])
+        assert out["status"] == abi.HS_FIT, case["name"]
+        assert [out["node"]] == case["want"]["NodeNames"], case["name"]
+        anno = out["annotations"]["hami.io/vgpu-devices-allocated"]
+        ids = [seg.split(",")[0] for ctr in anno.split(";") for seg in ctr.split(":") if "," in seg]
+        assert ids and ids[-1] in case["wantPodAnnotationDeviceIDs"], case["name"]
+        e.close()
