@@ -690,6 +690,12 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
   out->node_index = -1;
   const OpMeta& m = h->metas[op];
   if (m.status != HS_OK) { out->status = m.status; return; }
+  if (m.kind == OP_RELEASE) {
+    // deleting a pod whose Filter (earlier in this batch) found no node: podManager never held it
+    const DevPod& p = h->b_pods.h[op];
+    out->status = (p.rel_node < 0 && h->b_dec.h[p.rel_ref].status != 0) ? HS_ERR_NOTFOUND : HS_OK;
+    return;
+  }
   if (m.kind != OP_FILTER) { out->status = HS_OK; return; }
   const DevDecision& dec = h->b_dec.h[op];
   h->r_entries.clear(); h->r_annos.clear(); h->r_failed.clear();
