@@ -262,6 +262,14 @@ int32_t hs_run_batch(hs_handle* h, const hs_op* ops, uint32_t n_ops);
 /* Result i of the last hs_run_batch (DELETE ops yield status HS_OK, no node). */
 int32_t hs_batch_get(hs_handle* h, uint32_t i, hs_filter_result* out);
 
+/* Walk every result of the last hs_run_batch exactly as a caller would (node, score, the
+ * annotation map of scheduler.go:1124-1130, or FailedNodes) and fold it into one FNV-1a-64
+ * digest; also counts fits / no-fits.  The consumer a throughput measurement needs, and the
+ * "checksum of checksums" parity property at full size.  Layout of the digest: per op in order,
+ * status (4 B LE); fit: node name, score bits (4 B LE), then key\0value\0 per annotation in
+ * key order; no fit: node\0reason\0 per candidate in candidate order.                        */
+int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint64_t* digest);
+
 /* The reference undoes the commit when the annotation PATCH fails
  * (scheduler.go:1140-1147): podManager.DelPod + quota RmUsage.              */
 int32_t hs_rollback(hs_handle* h, const char* pod_uid);

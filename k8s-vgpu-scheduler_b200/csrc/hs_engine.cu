@@ -186,6 +186,7 @@ struct hs_handle {
   double last_ms = 0;
   uint64_t launches = 0;
   int block = 64;
+  bool no_fast = false;     // HS_NO_FAST=1: force the general evaluator (A/B testing of the two device paths)
 
   std::vector<VendorInfo> vendors;
   std::unordered_map<std::string, int> vendor_by_word;
@@ -221,7 +222,7 @@ struct hs_handle {
   DBuf<DevFail> b_fail;
   DBuf<uint32_t> b_counters;
   DBuf<int32_t> b_candpos;
-  uint32_t fail_cap = 8;
+  uint32_t fail_cap = 32;
   std::vector<OpMeta> metas;            // per device op
   std::vector<int> user_first_op;       // per caller op: index of its FILTER/RELEASE device op
   std::vector<int> user_status;
@@ -409,7 +410,7 @@ std::array<uint64_t, 4> entry_masks(hs_handle* h, const VendorInfo* v, const std
 }
 
 // use/no-use UUID annotation → sorted (node<<8 | mask8) words appended to the pool
-void uuid_words(hs_handle* h, const std::string& list, std::vector<uint32_t>& pool, uint32_t& off, uint32_t& cnt) {
+bool uuid_words(hs_handle* h, const std::string& list, std::vector<uint32_t>& pool, uint32_t& off, uint16_t& cnt) {
   std::map<uint32_t, uint32_t> per_node;
   for (auto& u0 : splitComma(list)) {
     std::string u = trimSpace(u0);
@@ -419,7 +420,9 @@ void uuid_words(hs_handle* h, const std::string& list, std::vector<uint32_t>& po
   }
   off = (uint32_t)pool.size();
   for (auto& kv : per_node) pool.push_back((kv.first << 8) | (kv.second & 255u));
-  cnt = (uint32_t)per_node.size();
+  if (per_node.size() > 65535) return false;
+  cnt = (uint16_t)per_node.size();
+  return true;
 }
 
 struct Compiled {
@@ -523,10 +526,10 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
         std::string list;
         if (get_anno(pod, v->use_uuid, list) && !trimSpace(list).empty()) {
           e.has_use = 1;
-          uuid_words(h, list, uuid_pool, e.use_off, e.use_cnt);
+          if (!uuid_words(h, list, uuid_pool, e.use_off, e.use_cnt)) { h->err = "use-uuid list spans too many nodes"; return HS_ERR_UNSUPPORTED; }
         }
         if (get_anno(pod, v->nouse_uuid, list) && !trimSpace(list).empty())
-          uuid_words(h, list, uuid_pool, e.nouse_off, e.nouse_cnt);
+          if (!uuid_words(h, list, uuid_pool, e.nouse_off, e.nouse_cnt)) { h->err = "no-use-uuid list spans too many nodes"; return HS_ERR_UNSUPPORTED; }
       }
       keyset.insert(ktype);
       if (v && v->ascend910) slotset.insert(ktype);
@@ -546,6 +549,13 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     c.entries[i].key_id = (uint8_t)std::distance(keyset.begin(), keyset.find(t));
     auto s = slotset.find(t);
     if (s != slotset.end()) c.entries[i].score_slot = (int8_t)std::distance(slotset.begin(), s);
+  }
+  if (!c.entries.empty()) {
+    p.e0 = c.entries[0];
+    const DevEntry& e = c.entries[0];
+    p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
+              !(e.flags & EF_ASCEND910)) ? 1 : 0;
+    if (h->no_fast) p.fast = 0;
   }
   c.meta.kind = OP_FILTER;
   c.meta.status = HS_OK;
@@ -675,7 +685,7 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
     alloc_base = h->b_counters.h[0];
     if (done < n_ops) {
       // resume: keep the alloc cursor, clear the fail cursor
-      h->b_counters.h[1] = 0; h->b_counters.h[2] = 0;
+      h->b_counters.h[1] = 0; h->b_counters.h[2] = 0; h->b_counters.h[3] = 0;
       CUDA_OK(h, cudaMemcpyAsync(h->b_counters.d, h->b_counters.h, 8 * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
   }
@@ -986,6 +996,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   h->modes = {"", "hami-core", "mig", "mps"};
   const char* blk = getenv("HS_BLOCK");
   if (blk) { int b = atoi(blk); if (b == 32 || b == 64 || b == 128) h->block = b; }
+  h->no_fast = getenv("HS_NO_FAST") != nullptr;
   const char* fc = getenv("HS_FAIL_CAP");
   if (fc && atoi(fc) > 0) h->fail_cap = (uint32_t)atoi(fc);
   if (grow_inventory(h, cfg && cfg->reserve_nodes ? (int)cfg->reserve_nodes : HS_TILE) != HS_OK) {
@@ -1226,6 +1237,42 @@ int32_t hs_batch_get(hs_handle* h, uint32_t i, hs_filter_result* out) {
   if (h->user_first_op[i] < 0) { out->status = HS_ERR_INVALID; return out->status; }
   assemble_result(h, h->user_first_op[i], out);
   return out->status;
+}
+
+static inline void fnv(uint64_t& hsh, const void* p, size_t n) {
+  const unsigned char* b = (const unsigned char*)p;
+  for (size_t i = 0; i < n; i++) { hsh ^= b[i]; hsh *= 1099511628211ull; }
+}
+static inline void fnv_str(uint64_t& hsh, const char* s) { fnv(hsh, s, strlen(s) + 1); }
+
+int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint64_t* digest) {
+  if (!h) return HS_ERR_INVALID;
+  uint64_t hsh = 1469598103934665603ull;
+  uint32_t fit = 0, nofit = 0;
+  hs_filter_result r;
+  for (size_t i = 0; i < h->user_first_op.size(); i++) {
+    h->r_strs.clear();
+    memset(&r, 0, sizeof r);
+    if (h->user_status[i] != HS_OK) r.status = h->user_status[i];
+    else if (h->user_first_op[i] < 0) r.status = HS_ERR_INVALID;
+    else assemble_result(h, h->user_first_op[i], &r);
+    int32_t st = r.status;
+    fnv(hsh, &st, 4);
+    if (h->user_first_op[i] >= 0 && h->metas[h->user_first_op[i]].kind != OP_FILTER) continue;
+    if (st == HS_FIT) {
+      fit++;
+      fnv_str(hsh, r.node_name);
+      fnv(hsh, &r.score, 4);
+      for (uint32_t a = 0; a < r.n_annotations; a++) { fnv_str(hsh, r.annotations[a].key); fnv_str(hsh, r.annotations[a].value); }
+    } else if (st == HS_NOFIT) {
+      nofit++;
+      for (uint32_t f = 0; f < r.n_failed; f++) { fnv_str(hsh, r.failed[f].node); fnv_str(hsh, r.failed[f].reason); }
+    }
+  }
+  if (n_fit) *n_fit = fit;
+  if (n_nofit) *n_nofit = nofit;
+  if (digest) *digest = hsh;
+  return HS_OK;
 }
 
 int32_t hs_snapshot_node(hs_handle* h, const char* node, hs_device_usage_row* rows, uint32_t cap) {

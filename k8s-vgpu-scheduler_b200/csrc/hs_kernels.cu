@@ -19,12 +19,12 @@
 //
 // Integer/compare work on CUDA cores: there is no dense contraction on this path,
 // so no tensor cores.
-#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
 #include "hs_eval.cuh"
+#include "hs_fast.cuh"
 
-namespace cg = cooperative_groups;
+
 
 __device__ __forceinline__ void load_node(const KernelArgs& ka, int node, uint32_t nflags, NodeWork& w) {
   const int tile = node / HS_TILE, lane = node % HS_TILE;
@@ -114,135 +114,256 @@ __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
   f.c0 = c0; f.c1 = c1; f.pad = 0;
 }
 
-extern "C" __global__ void __launch_bounds__(128)
+// ---- grid-wide barrier ---------------------------------------------------------------------------
+// One arrival counter in L2, never reset inside a launch: barrier k completes when it reaches
+// (k+1) * gridDim.x.  The launch is cooperative, so every CTA is resident.  Thread 0 publishes this
+// CTA's arg-best (atomicMax) before its release-add, polls with relaxed loads (no L1 invalidation
+// inside the spin), then performs one acquire load.
+__device__ __forceinline__ void grid_barrier(uint32_t* arrive, uint32_t expected) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(arrive) : "memory");
+    uint32_t v;
+    do {
+      asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(arrive) : "memory");
+    } while (v < expected);
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(arrive) : "memory");
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// ---- request staging: the next op's 160 B record is prefetched with cp.async while the current
+// op is evaluated (two shared-memory buffers).
+__device__ __forceinline__ void prefetch_op(const DevPod* src, DevPod* dst) {
+  if (threadIdx.x < sizeof(DevPod) / 16) {
+    const uint32_t s = (uint32_t)__cvta_generic_to_shared(reinterpret_cast<char*>(dst) + threadIdx.x * 16);
+    const char* g = reinterpret_cast<const char*>(src) + threadIdx.x * 16;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(g) : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void prefetch_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ void load_regs(const KernelArgs& ka, int node, NodeRegs& n) {
+  const int tile = node / HS_TILE, lane = node % HS_TILE;
+  const int4* dy = ka.dyn + (size_t)tile * HS_D * HS_TILE + lane;
+  const int4* st = ka.stat + (size_t)tile * HS_D * HS_TILE + lane;
+  int4 a[HS_D], b[HS_D];
+#pragma unroll
+  for (int d = 0; d < HS_D; d++) { a[d] = dy[d * HS_TILE]; b[d] = __ldg(st + d * HS_TILE); }
+#pragma unroll
+  for (int d = 0; d < HS_D; d++) {
+    n.used[d] = a[d].x; n.mem[d] = a[d].y; n.cores[d] = a[d].z; n.dflags[d] = (uint32_t)a[d].w;
+    n.count[d] = b[d].x; n.totmem[d] = b[d].y; n.totcore[d] = b[d].z; n.packed[d] = (uint32_t)b[d].w;
+  }
+}
+
+__device__ __forceinline__ void regs_to_work(const NodeRegs& n, uint32_t nflags, NodeWork& w) {
+#pragma unroll
+  for (int d = 0; d < HS_D; d++) {
+    w.used[d] = n.used[d]; w.mem[d] = n.mem[d]; w.cores[d] = n.cores[d]; w.dflags[d] = n.dflags[d];
+    w.count[d] = n.count[d]; w.totmem[d] = n.totmem[d]; w.totcore[d] = n.totcore[d]; w.packed[d] = n.packed[d];
+  }
+  w.ndev = NF_NDEV(nflags);
+  w.order = 0x76543210u;
+}
+
+extern "C" __global__ void __launch_bounds__(128, 1)
 hs_decide_kernel(const KernelArgs ka) {
-  cg::grid_group grid = cg::this_grid();
-  __shared__ DevPod s_pod;
-  __shared__ DevEntry s_ent[HS_MAX_E];
+  __shared__ __align__(16) DevPod s_op[2];
+  __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
   __shared__ unsigned long long s_red[4];
 
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
   const int gsize = gridDim.x * blockDim.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const bool resident = ka.n_nodes <= gsize;  // every thread owns at most one node: keep it loaded
+  const bool resident = ka.n_nodes <= gsize;  // every thread owns at most one node: it stays in registers
 
-  NodeWork w;
+  NodeRegs reg;                // the owned node (resident mode): usage kept current by this thread's own commits
   uint32_t my_flags = 0;
   int my_pos = -1;
+#pragma unroll
+  for (int d = 0; d < HS_D; d++) {
+    reg.used[d] = reg.mem[d] = reg.cores[d] = reg.count[d] = reg.totmem[d] = reg.totcore[d] = 0;
+    reg.packed[d] = reg.dflags[d] = 0;
+  }
   if (resident && gtid < ka.n_nodes) {
     my_flags = ka.node_flags[gtid];
-    load_node(ka, gtid, my_flags, w);
+    load_regs(ka, gtid, reg);
     if (my_flags & NF_ALIVE) my_pos = ka.cand_pos ? ka.cand_pos[gtid] : gtid;
   }
-  // base usage of the owned node (resident mode), updated by this thread's own commits/releases
-  int bu[HS_D], bm[HS_D], bc[HS_D];
-#pragma unroll
-  for (int d = 0; d < HS_D; d++) { bu[d] = w.used[d]; bm[d] = w.mem[d]; bc[d] = w.cores[d]; }
 
-  DevAlloc la[HS_MAX_ALLOC];   // picks of this thread's best node for the current op
+  DevAlloc la[HS_MAX_ALLOC];   // general path: picks of this thread's best node for the current op
   uint32_t fail_count = 0;     // no-fit decisions so far: identical in every thread
+  uint32_t barriers = 0;       // grid barriers executed in this launch: identical in every thread
   int r = ka.op_begin;
+  if (r < ka.n_ops) prefetch_op(ka.pods + r, &s_op[0]);
 
   for (; r < ka.n_ops; r++) {
-    __syncthreads();
-    {  // stage the op in shared memory
-      const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.pods + r);
-      uint32_t* dst = reinterpret_cast<uint32_t*>(&s_pod);
-      for (int i = threadIdx.x; i < (int)(sizeof(DevPod) / 4); i += blockDim.x) dst[i] = src[i];
-    }
-    __syncthreads();
-    {
-      const int ne = s_pod.n_entries;
-      const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.entries + s_pod.entry_off);
-      uint32_t* dst = reinterpret_cast<uint32_t*>(s_ent);
-      for (int i = threadIdx.x; i < ne * (int)(sizeof(DevEntry) / 4); i += blockDim.x) dst[i] = src[i];
-    }
-    __syncthreads();
+    const int buf = (r - ka.op_begin) & 1;
+    prefetch_wait();
+    __syncthreads();             // op r is staged; every thread is done with the other buffer and with s_ent
+    if (r + 1 < ka.n_ops) prefetch_op(ka.pods + r + 1, &s_op[buf ^ 1]);
+    const DevPod& pod = s_op[buf];
 
-    if (s_pod.op == OP_RELEASE) {
-      // podManager.DelPod + usage release (scheduler.go:226-253): the owner subtracts what the commit added
-      int node = s_pod.rel_node;
+    if (pod.op == OP_RELEASE) {
+      // podManager.DelPod + usage release (scheduler.go:226-253): the owner subtracts what the commit added.
+      // An in-batch reference is only trusted by the thread that wrote that decision (its own stores).
+      int node = pod.rel_node;
       const int4* rows;
-      if (node >= 0) rows = ka.rel_pool + s_pod.rel_off;
+      if (node >= 0) rows = ka.rel_pool + pod.rel_off;
       else {
-        node = ka.decisions[s_pod.rel_ref].node;  // written before an earlier barrier
-        rows = ka.commit_delta + (size_t)s_pod.rel_ref * HS_D;
-        if (ka.decisions[s_pod.rel_ref].status != 0) node = -1;
+        node = ka.decisions[pod.rel_ref].node;
+        rows = ka.commit_delta + (size_t)pod.rel_ref * HS_D;
+        if (ka.decisions[pod.rel_ref].status != 0) node = -1;
       }
-      if (node >= 0 && (node % gsize) == gtid) {
+      if (node >= 0 && node < ka.n_nodes && (node % gsize) == gtid) {
         int4 delta[HS_D];
+#pragma unroll
         for (int d = 0; d < HS_D; d++) delta[d] = rows[d];
         store_usage(ka, node, delta, -1);
-        if (resident)
-          for (int d = 0; d < HS_D; d++) { bu[d] -= delta[d].x; bm[d] -= delta[d].y; bc[d] -= delta[d].z; }
+        if (resident) {
+#pragma unroll
+          for (int d = 0; d < HS_D; d++) { reg.used[d] -= delta[d].x; reg.mem[d] -= delta[d].y; reg.cores[d] -= delta[d].z; }
+        }
       }
-      if (gtid == 0) { ka.decisions[r].status = 2; ka.decisions[r].node = node; ka.decisions[r].n_alloc = 0; }
+      if (gtid == 0) { ka.decisions[r].status = 2; ka.decisions[r].n_alloc = 0; }
       continue;
     }
-    if (s_pod.op != OP_FILTER) {
+    if (pod.op != OP_FILTER) {
       if (gtid == 0) { ka.decisions[r].status = 2; ka.decisions[r].node = -1; ka.decisions[r].n_alloc = 0; }
       continue;
     }
 
+    const bool spread = pod.flags & PF_NODE_SPREAD;
+    const bool fast = pod.fast != 0;
+    const DevEntry* ent = &pod.e0;
+    if (pod.n_entries > 1) {     // general path with several entries: fetch them from the pool
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.entries + pod.entry_off);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(s_ent);
+      for (int i = threadIdx.x; i < pod.n_entries * (int)(sizeof(DevEntry) / 4); i += blockDim.x) dst[i] = src[i];
+      __syncthreads();
+      ent = s_ent;
+    }
+
     // ---- sweep: evaluate owned nodes --------------------------------------------------------
-    const bool spread = s_pod.flags & PF_NODE_SPREAD;
     unsigned long long my_key = 0;
     int my_node = -1;
     float my_score = 0.0f;
     uint32_t my_nalloc = 0;
-    EvalOut out;
-    if (resident) {
-      if (my_pos >= 0) {
-#pragma unroll
-        for (int d = 0; d < HS_D; d++) { w.used[d] = bu[d]; w.mem[d] = bm[d]; w.cores[d] = bc[d]; }
-        out.allocs = la; out.n_alloc = 0;
-        float sc;
-        if (dev_score_node<EV_RECORD>(w, s_pod, s_ent, (uint32_t)gtid, my_flags, ka, out, &sc)) {
-          my_key = make_key(sc, spread, (uint32_t)(ka.pos_base + my_pos));
-          my_node = gtid; my_score = sc; my_nalloc = out.n_alloc;
+    FastEval fe;
+    fe.cand = 0; fe.qpos = 0; fe.cores = 0;
+    if (fast) {
+      if (resident) {
+        if (my_pos >= 0 && fast_fit(reg, (uint32_t)gtid, my_flags, pod, pod.e0, ka, fe)) {
+          my_score = fast_node_score(reg);
+          my_key = make_key(my_score, spread, (uint32_t)(ka.pos_base + my_pos));
+          my_node = gtid;
+        }
+      } else {
+        NodeRegs n;
+        FastEval f2;
+        for (int node = gtid; node < ka.n_nodes; node += gsize) {
+          const uint32_t nf = ka.node_flags[node];
+          if (!(nf & NF_ALIVE)) continue;
+          const int pos = ka.cand_pos ? ka.cand_pos[node] : node;
+          if (pos < 0) continue;
+          load_regs(ka, node, n);
+          if (fast_fit(n, (uint32_t)node, nf, pod, pod.e0, ka, f2)) {
+            const float sc = fast_node_score(n);
+            const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
+            if (key > my_key) { my_key = key; my_node = node; my_score = sc; }
+          }
         }
       }
     } else {
-      DevAlloc tmp[HS_MAX_ALLOC];
-      for (int node = gtid; node < ka.n_nodes; node += gsize) {
-        const uint32_t nf = ka.node_flags[node];
-        if (!(nf & NF_ALIVE)) continue;
-        const int pos = ka.cand_pos ? ka.cand_pos[node] : node;
-        if (pos < 0) continue;
-        load_node(ka, node, nf, w);
-        out.allocs = tmp; out.n_alloc = 0;
-        float sc;
-        if (dev_score_node<EV_RECORD>(w, s_pod, s_ent, (uint32_t)node, nf, ka, out, &sc)) {
-          const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
-          if (key > my_key) {
-            my_key = key; my_node = node; my_score = sc; my_nalloc = out.n_alloc;
-            for (uint32_t i = 0; i < out.n_alloc; i++) la[i] = tmp[i];
+      NodeWork w;
+      EvalOut out;
+      if (resident) {
+        if (my_pos >= 0) {
+          regs_to_work(reg, my_flags, w);
+          out.allocs = la; out.n_alloc = 0;
+          float sc;
+          if (dev_score_node<EV_RECORD>(w, pod, ent, (uint32_t)gtid, my_flags, ka, out, &sc)) {
+            my_key = make_key(sc, spread, (uint32_t)(ka.pos_base + my_pos));
+            my_node = gtid; my_score = sc; my_nalloc = out.n_alloc;
+          }
+        }
+      } else {
+        DevAlloc tmp[HS_MAX_ALLOC];
+        for (int node = gtid; node < ka.n_nodes; node += gsize) {
+          const uint32_t nf = ka.node_flags[node];
+          if (!(nf & NF_ALIVE)) continue;
+          const int pos = ka.cand_pos ? ka.cand_pos[node] : node;
+          if (pos < 0) continue;
+          load_node(ka, node, nf, w);
+          out.allocs = tmp; out.n_alloc = 0;
+          float sc;
+          if (dev_score_node<EV_RECORD>(w, pod, ent, (uint32_t)node, nf, ka, out, &sc)) {
+            const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
+            if (key > my_key) {
+              my_key = key; my_node = node; my_score = sc; my_nalloc = out.n_alloc;
+              for (uint32_t i = 0; i < out.n_alloc; i++) la[i] = tmp[i];
+            }
           }
         }
       }
     }
 
-    // ---- arg-best: warp shuffle, then one atomicMax per CTA ----------------------------------
+    // ---- arg-best: warp shuffle, one atomicMax per CTA, ONE grid barrier -----------------------
     unsigned long long bk = warp_max_u64(my_key);
-    if (lane == 0) s_red[warp] = bk;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      for (int i = 1; i < (int)(blockDim.x >> 5); i++) bk = s_red[i] > bk ? s_red[i] : bk;
-      if (bk) atomicMax(ka.best + r, bk);
+    if (blockDim.x > 32) {
+      if (lane == 0) s_red[warp] = bk;
+      __syncthreads();
+      if (threadIdx.x == 0)
+        for (int i = 1; i < (int)(blockDim.x >> 5); i++) bk = s_red[i] > bk ? s_red[i] : bk;
     }
-    grid.sync();
-    const unsigned long long win = *reinterpret_cast<volatile unsigned long long*>(ka.best + r);
+    if (threadIdx.x == 0 && bk) atomicMax(ka.best + r, bk);
+    barriers++;
+    grid_barrier(ka.counters + 3, barriers * gridDim.x);
+    const unsigned long long win = ld_relaxed_u64(ka.best + r);
 
     if (win != 0) {
       if (my_key == win) {
         // ---- commit (owner only) -----------------------------------------------------------
+        int4 delta[HS_D];
+        if (fast) {
+          const uint32_t nf = resident ? my_flags : ka.node_flags[my_node];
+          if (!resident) {   // streaming mode: re-derive the winner's picks (reg is free in this mode)
+            load_regs(ka, my_node, reg);
+            fast_fit(reg, (uint32_t)my_node, nf, pod, pod.e0, ka, fe);
+          }
+          int picks[HS_D];
+          const int np = fast_pick((uint32_t)my_node, nf, pod, pod.e0, ka, fe, picks);
+          my_nalloc = (uint32_t)np;
+#pragma unroll
+          for (int d = 0; d < HS_D; d++) delta[d] = make_int4(0, 0, 0, 0);
+          for (int i = 0; i < np; i++) {
+            const int s = picks[i];
+            int memreq = 0;
+#pragma unroll
+            for (int d = 0; d < HS_D; d++) if (d == s) memreq = fe.memreq[d];
+            la[i].entry = 0; la[i].dev = (uint8_t)s; la[i].usedcores = (int16_t)fe.cores; la[i].usedmem = memreq;
+#pragma unroll
+            for (int d = 0; d < HS_D; d++) if (d == s) delta[d] = make_int4(1, memreq, fe.cores, 0);
+          }
+        } else {
+          collapse_rows(ent, la, my_nalloc, delta);
+        }
         const uint32_t off = atomicAdd(ka.counters + 0, my_nalloc);
         for (uint32_t i = 0; i < my_nalloc && off + i < ka.alloc_cap; i++) ka.allocs[off + i] = la[i];
-        int4 delta[HS_D];
-        collapse_rows(s_ent, la, my_nalloc, delta);
         store_usage(ka, my_node, delta, +1);
-        if (resident)
-          for (int d = 0; d < HS_D; d++) { bu[d] += delta[d].x; bm[d] += delta[d].y; bc[d] += delta[d].z; }
+        if (resident) {
+#pragma unroll
+          for (int d = 0; d < HS_D; d++) { reg.used[d] += delta[d].x; reg.mem[d] += delta[d].y; reg.cores[d] += delta[d].z; }
+        }
+#pragma unroll
         for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)r * HS_D + d] = delta[d];
         DevDecision dec;
         dec.status = 0; dec.node = my_node; dec.score = my_score; dec.alloc_off = off; dec.n_alloc = my_nalloc;
@@ -253,21 +374,19 @@ hs_decide_kernel(const KernelArgs ka) {
       // ---- no node fits: per-node reasons for FailedNodes (scheduler.go:1109-1114) ------------
       if (fail_count >= ka.fail_cap) break;  // fail buffer full: the host drains it and resumes at op r
       DevFail* fb = ka.fail + (size_t)fail_count * ka.n_nodes;
+      NodeWork w;
+      EvalOut out;
       for (int node = gtid; node < ka.n_nodes; node += gsize) {
         const uint32_t nf = ka.node_flags[node];
         DevFail f;
         f.kind_cards = FK_NOT_CANDIDATE; f.c0 = f.c1 = f.pad = 0;
         const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
         if (pos >= 0) {
-          if (resident) {
-#pragma unroll
-            for (int d = 0; d < HS_D; d++) { w.used[d] = bu[d]; w.mem[d] = bm[d]; w.cores[d] = bc[d]; }
-          } else {
-            load_node(ka, node, nf, w);
-          }
+          if (resident) regs_to_work(reg, nf, w);
+          else load_node(ka, node, nf, w);
           out.fkind = FK_NONE; out.fcards = 0;
           float sc;
-          dev_score_node<EV_EXPLAIN>(w, s_pod, s_ent, (uint32_t)node, nf, ka, out, &sc);
+          dev_score_node<EV_EXPLAIN>(w, pod, ent, (uint32_t)node, nf, ka, out, &sc);
           pack_fail(out, f);
         }
         fb[node] = f;
@@ -281,6 +400,7 @@ hs_decide_kernel(const KernelArgs ka) {
       fail_count++;
     }
   }
+  prefetch_wait();
   if (gtid == 0) { ka.counters[2] = (uint32_t)r; ka.counters[1] = fail_count; }
 }
 

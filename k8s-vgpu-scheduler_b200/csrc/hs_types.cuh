@@ -56,13 +56,12 @@ struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 
   uint32_t mode_allow;      // bit m: nvidia.com/vgpu-mode contains mode m         (nvidia/device.go:495-498)
   uint16_t vendor;          // HV_*; HV_NONE → "Device type not found"
   uint16_t flags;
-  uint32_t use_off, use_cnt;     // sorted (node<<8 | mask8) words in the uuid pool: use-uuid list
-  uint32_t nouse_off, nouse_cnt; // same for the no-use list
+  uint32_t use_off, nouse_off;   // sorted (node<<8 | mask8) words in the uuid pool: use-uuid / no-use-uuid lists
+  uint16_t use_cnt, nouse_cnt;
   int8_t score_slot;        // ScoreNode accumulator (Ascend910*), -1 none
   uint8_t has_use;          // a non-empty use-uuid annotation exists
   uint8_t key_id;           // id of k.Type among the pod's distinct type keys (PodDevices key)
   uint8_t is_init;          // entry belongs to an init container
-  uint32_t pad2;
 };
 
 // pod flags
@@ -79,7 +78,8 @@ struct DevPod {             // one op of the stream, 96 B + entries
   uint32_t flags;           // PF_*
   uint8_t sort_mode;        // SORT_*
   uint8_t chain[3];         // CK_* keys in order (SORT_CHAIN)
-  uint8_t n_ctr, n_init, n_entries, pad;
+  uint8_t n_ctr, n_init, n_entries;
+  uint8_t fast;             // exactly one request entry of the common shape: register-resident path (hs_fast.cuh)
   float w_slot, w_core, w_mem;   // float32(int64 weight)
   uint32_t entry_off;       // first DevEntry in the entry pool
   uint8_t ctr_begin[HS_MAX_C + 1]; // container c owns entries [ctr_begin[c], ctr_begin[c+1])
@@ -88,8 +88,11 @@ struct DevPod {             // one op of the stream, 96 B + entries
   int32_t rel_node;         // node slot, or -1 = take node and deltas from decision `rel_ref` of this batch
   int32_t rel_ref;
   int32_t rel_off;          // first of HS_D {slots, mem, cores, 0} int4 rows in the release pool
-  uint32_t pad4[4];
+  uint32_t pad4[8];
+  DevEntry e0;              // the first (usually only) entry rides inside the op record: one 160 B prefetch per op
 };
+static_assert(sizeof(DevEntry) == 64, "DevEntry layout");
+static_assert(sizeof(DevPod) == 160, "DevPod layout: 96 B header + 64 B first entry, 16 B chunks for cp.async");
 
 struct DevAlloc {           // one ContainerDevice, 8 B
   uint8_t entry;            // index into the pod's entries (container + type)

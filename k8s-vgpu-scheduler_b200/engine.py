@@ -17,7 +17,7 @@ _lib = None
 EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_batch_get", "hs_rollback",
-    "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count",
+    "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary",
 ]
 
 
@@ -43,6 +43,7 @@ def lib():
     L.hs_filter.argtypes = [C.c_void_p, P(abi.hs_pod), P(C.c_char_p), C.c_uint32, P(abi.hs_filter_result)]
     L.hs_run_batch.argtypes = [C.c_void_p, P(abi.hs_op), C.c_uint32]
     L.hs_batch_get.argtypes = [C.c_void_p, C.c_uint32, P(abi.hs_filter_result)]
+    L.hs_batch_summary.argtypes = [C.c_void_p, P(C.c_uint32), P(C.c_uint32), P(C.c_uint64)]
     L.hs_rollback.argtypes = [C.c_void_p, C.c_char_p]
     L.hs_snapshot_node.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_device_usage_row), C.c_uint32]
     L.hs_last_device_ms.restype = C.c_double
@@ -142,6 +143,12 @@ class Engine:
 
     def batch_get_raw(self, i, res):
         return self.L.hs_batch_get(self.h, i, C.byref(res))
+
+    def batch_summary(self):
+        """(n_fit, n_nofit, digest) over every result of the last run_batch."""
+        nf, nn, dg = C.c_uint32(), C.c_uint32(), C.c_uint64()
+        self._check(self.L.hs_batch_summary(self.h, C.byref(nf), C.byref(nn), C.byref(dg)))
+        return nf.value, nn.value, dg.value
 
     def snapshot(self, node, cap=16):
         rows = (abi.hs_device_usage_row * cap)()

@@ -1,6 +1,7 @@
 // oracle_capi.cc — TEST INFRASTRUCTURE ONLY.  ctypes-facing wrapper over oracle.cc.
 #include "oracle_capi.h"
 
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <deque>
@@ -178,6 +179,51 @@ int32_t oracle_filter(oracle_handle* o, const hs_pod* pod, const char* const* no
     out->status = HS_ERR_UNSUPPORTED;
     return HS_ERR_UNSUPPORTED;
   }
+}
+
+static inline void fnv(uint64_t& hsh, const void* p, size_t n) {
+  const unsigned char* b = (const unsigned char*)p;
+  for (size_t i = 0; i < n; i++) { hsh ^= b[i]; hsh *= 1099511628211ull; }
+}
+static inline void fnv_str(uint64_t& hsh, const std::string& s) { fnv(hsh, s.c_str(), s.size() + 1); }
+
+int32_t oracle_run_ops(oracle_handle* o, const hs_op* ops, uint32_t n_ops, uint32_t* n_fit, uint32_t* n_nofit,
+                       uint64_t* digest, double* seconds) {
+  uint64_t hsh = 1469598103934665603ull;
+  uint32_t fit = 0, nofit = 0;
+  auto t0 = std::chrono::steady_clock::now();
+  try {
+    for (uint32_t i = 0; i < n_ops; i++) {
+      if (ops[i].kind == HS_OP_DELETE) {
+        int32_t st = o->s->DeletePod(str(ops[i].pod->uid)) ? HS_OK : HS_ERR_NOTFOUND;
+        fnv(hsh, &st, 4);
+        continue;
+      }
+      Pod p = toPod(ops[i].pod);
+      FilterResult fr = o->s->Filter(p, nullptr);
+      int32_t st = fr.status;
+      fnv(hsh, &st, 4);
+      if (st == HS_FIT) {
+        fit++;
+        fnv_str(hsh, fr.chosen.NodeID);
+        float sc = fr.chosen.Score;
+        fnv(hsh, &sc, 4);
+        for (auto& kv : fr.annotations) { fnv_str(hsh, kv.first); fnv_str(hsh, kv.second); }
+      } else if (st == HS_NOFIT) {
+        nofit++;
+        for (auto& f : fr.failedNodes) { fnv_str(hsh, f.first); fnv_str(hsh, f.second); }
+      }
+    }
+  } catch (std::exception& e) {
+    o->err = e.what();
+    return HS_ERR_UNSUPPORTED;
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  if (n_fit) *n_fit = fit;
+  if (n_nofit) *n_nofit = nofit;
+  if (digest) *digest = hsh;
+  if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+  return HS_OK;
 }
 
 int32_t oracle_snapshot_node(oracle_handle* o, const char* node, hs_device_usage_row* rows, uint32_t cap) {

@@ -42,6 +42,10 @@ int32_t oracle_filter(oracle_handle* o, const hs_pod* pod, const char* const* no
                       hs_filter_result* out);
 int32_t oracle_snapshot_node(oracle_handle* o, const char* node, hs_device_usage_row* rows, uint32_t cap);
 const char* oracle_last_error(const oracle_handle* o);
+/* Run a whole op stream sequentially (Filter / DeletePod) and fold the results into the same FNV-1a-64
+ * digest hs_batch_summary computes (see include/hami_sched.h).  seconds = wall time of the loop. */
+int32_t oracle_run_ops(oracle_handle* o, const hs_op* ops, uint32_t n_ops, uint32_t* n_fit, uint32_t* n_nofit,
+                       uint64_t* digest, double* seconds);
 
 /* scoreNode (score.go:294-346) on an explicit NodeUsage, as Test_calcScore drives it.
  * list_policy NULL / numa_bind <0: derive from the pod like buildNodeUsage. status HS_FIT or HS_NOFIT (failed[0].reason). */

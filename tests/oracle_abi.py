@@ -45,6 +45,8 @@ def lib():
     L.oracle_pod_delete.argtypes = [C.c_void_p, C.c_char_p]
     L.oracle_filter.argtypes = [C.c_void_p, P(abi.hs_pod), P(C.c_char_p), C.c_uint32, P(abi.hs_filter_result)]
     L.oracle_snapshot_node.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_device_usage_row), C.c_uint32]
+    L.oracle_run_ops.argtypes = [C.c_void_p, P(abi.hs_op), C.c_uint32, P(C.c_uint32), P(C.c_uint32), P(C.c_uint64),
+                                 P(C.c_double)]
     L.oracle_last_error.restype = C.c_char_p
     L.oracle_last_error.argtypes = [C.c_void_p]
     L.oracle_score_node.argtypes = [C.c_void_p, C.c_char_p, P(oracle_dev), C.c_uint32, C.c_char_p, C.c_int32,
@@ -140,6 +142,14 @@ class Oracle:
         if rc < 0:
             out["error"] = self.L.oracle_last_error(self.h).decode()
         return out
+
+    def run_ops(self, packed):
+        """packed: engine.PackedOps.  Returns (n_fit, n_nofit, digest, seconds)."""
+        nf, nn, dg, sec = C.c_uint32(), C.c_uint32(), C.c_uint64(), C.c_double()
+        rc = self.L.oracle_run_ops(self.h, packed.arr, packed.n, C.byref(nf), C.byref(nn), C.byref(dg), C.byref(sec))
+        if rc != 0:
+            raise RuntimeError(self.L.oracle_last_error(self.h).decode())
+        return nf.value, nn.value, dg.value, sec.value
 
     def snapshot(self, node, cap=16):
         rows = (abi.hs_device_usage_row * cap)()
