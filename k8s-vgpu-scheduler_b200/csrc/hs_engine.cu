@@ -185,7 +185,7 @@ struct hs_handle {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   double last_ms = 0;
   uint64_t launches = 0;
-  int block = 64;
+  int block = 256;          // threads per CTA of the decide kernel: 8 lanes per node
   bool no_fast = false;     // HS_NO_FAST=1: force the general evaluator (A/B testing of the two device paths)
 
   std::vector<VendorInfo> vendors;
@@ -218,10 +218,12 @@ struct hs_handle {
   DBuf<DevDecision> b_dec;
   DBuf<DevAlloc> b_alloc;
   DBuf<int4> b_delta;
-  DBuf<unsigned long long> b_best;
+  DBuf<OpSync> b_best;
   DBuf<DevFail> b_fail;
   DBuf<uint32_t> b_counters;
   DBuf<int32_t> b_candpos;
+  DBuf<unsigned long long> b_timing;   // HS_TIMING=1: phase clocks of block 0
+  bool timing = false;
   uint32_t fail_cap = 32;
   std::vector<OpMeta> metas;            // per device op
   std::vector<int> user_first_op;       // per caller op: index of its FILTER/RELEASE device op
@@ -329,7 +331,7 @@ int grow_inventory(hs_handle* h, int need_nodes) {
   return HS_OK;
 }
 
-inline size_t inv_idx(int node, int d) { return ((size_t)(node / HS_TILE) * HS_D + d) * HS_TILE + (node % HS_TILE); }
+inline size_t inv_idx(int node, int d) { return (size_t)node * HS_D + d; }   // node-major SoA (hs_kernels.cu)
 
 void mark_dirty(hs_handle* h, int node) {
   int t = node / HS_TILE;
@@ -616,10 +618,11 @@ int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_ca
   ka.pods = h->b_pods.d; ka.entries = h->b_entries.d; ka.uuid_pool = h->b_uuid.d; ka.rel_pool = h->b_rel.d;
   ka.n_ops = n_ops;
   ka.decisions = h->b_dec.d; ka.allocs = h->b_alloc.d; ka.alloc_cap = alloc_cap;
-  ka.commit_delta = h->b_delta.d; ka.best = h->b_best.d;
+  ka.commit_delta = h->b_delta.d; ka.sync = h->b_best.d;
   ka.fail = h->b_fail.d; ka.fail_cap = h->fail_cap;
   ka.counters = h->b_counters.d;
   ka.pos_base = 0;
+  ka.timing = h->timing ? h->b_timing.d : nullptr;
   return HS_OK;
 }
 
@@ -640,13 +643,13 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
   if (n_rel) CUDA_OK(h, cudaMemcpyAsync(h->b_rel.d, h->b_rel.h, n_rel * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
   if (h->have_cand) CUDA_OK(h, cudaMemcpyAsync(h->b_candpos.d, h->b_candpos.h, (size_t)n_nodes * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
   CUDA_OK(h, cudaMemsetAsync(h->b_dec.d, 0xff, (size_t)n_ops * sizeof(DevDecision), h->stream));
-  CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, (size_t)n_ops * sizeof(unsigned long long), h->stream));
+  CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, (size_t)n_ops * sizeof(OpSync), h->stream));
   CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
 
   int block = h->block;
   int maxb = hs_decide_max_blocks(block, h->device);
   if (maxb <= 0) { h->err = "hs_decide_kernel cannot be launched cooperatively on this device"; return HS_ERR_CUDA; }
-  int grid = std::min(maxb, std::max(1, (n_nodes + block - 1) / block));
+  int grid = std::min(maxb, std::max(1, (n_nodes * HS_D + block - 1) / block));   // 8 lanes per node when it fits
 
   h->fail_host.clear();
   h->op_fail_slot.assign(n_ops, 0xffffffffu);
@@ -686,6 +689,7 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
     if (done < n_ops) {
       // resume: keep the alloc cursor, clear the fail cursor
       h->b_counters.h[1] = 0; h->b_counters.h[2] = 0; h->b_counters.h[3] = 0;
+      CUDA_OK(h, cudaMemsetAsync(h->b_best.d + done, 0, sizeof(OpSync), h->stream));  // op `done` runs again
       CUDA_OK(h, cudaMemcpyAsync(h->b_counters.d, h->b_counters.h, 8 * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
   }
@@ -995,8 +999,9 @@ hs_handle* hs_create(const hs_config* cfg) {
     }
   h->modes = {"", "hami-core", "mig", "mps"};
   const char* blk = getenv("HS_BLOCK");
-  if (blk) { int b = atoi(blk); if (b == 32 || b == 64 || b == 128) h->block = b; }
+  if (blk) { int b = atoi(blk); if (b >= 32 && b <= 512 && b % 32 == 0) h->block = b; }
   h->no_fast = getenv("HS_NO_FAST") != nullptr;
+  if (getenv("HS_TIMING") && h->b_timing.ensure(16)) { h->timing = true; cudaMemset(h->b_timing.d, 0, 16 * sizeof(unsigned long long)); }
   const char* fc = getenv("HS_FAIL_CAP");
   if (fc && atoi(fc) > 0) h->fail_cap = (uint32_t)atoi(fc);
   if (grow_inventory(h, cfg && cfg->reserve_nodes ? (int)cfg->reserve_nodes : HS_TILE) != HS_OK) {
@@ -1290,6 +1295,21 @@ int32_t hs_snapshot_node(hs_handle* h, const char* node, hs_device_usage_row* ro
     rows[d].used = v.x; rows[d].usedmem = v.y; rows[d].usedcores = v.z;
   }
   return n;
+}
+
+extern "C" long long hs_launch_divcheck(unsigned long long n, unsigned long long seed);
+/* Self-check: the branch-free float32 divide of the fast path vs the IEEE divide on n operand pairs
+ * (the first 2^24 are an exhaustive small grid, the rest pseudo-random int32 pairs). Returns mismatches. */
+long long hs_debug_divcheck(unsigned long long n, unsigned long long seed) { return hs_launch_divcheck(n, seed); }
+
+/* Diagnostic (HS_TIMING=1): cumulative SM clocks block 0 spent per phase of the decide loop:
+ * 0 stage, 1 release ops, 2 sweep, 3 reduce, 4 barrier, 5 winner read, 6 commit/explain. */
+int32_t hs_debug_timing(hs_handle* h, unsigned long long out[8]) {
+  if (!h || !h->timing) return HS_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (cudaMemcpy(h->b_timing.h, h->b_timing.d, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) return HS_ERR_CUDA;
+  for (int i = 0; i < 8; i++) out[i] = h->b_timing.h[i];
+  return HS_OK;
 }
 
 double hs_last_device_ms(const hs_handle* h) { return h ? h->last_ms : 0.0; }

@@ -1,38 +1,38 @@
 // hs_kernels.cu — sm_100a kernels of the HAMi Filter/Score engine.
 //
-// hs_decide_kernel is ONE persistent cooperative kernel that runs a whole stream
-// of scheduling ops in order.  Per FILTER op (reference: Scheduler.Filter,
-// pkg/scheduler/scheduler.go:1067-1154):
-//   1. the op's request descriptor is staged in shared memory;
-//   2. every thread evaluates the node(s) it owns (hs_eval.cuh: ComputeScore, the
-//      stable device sort, the vendor Fit scan, ComputeDefaultScore) reading the
-//      SoA inventory with coalesced 128-bit loads — or, when every thread owns at
-//      most one node, from its registers/local copy loaded once per launch;
-//   3. warp-shuffle + shared-memory arg-best, one 64-bit atomicMax per CTA;
-//   4. ONE grid barrier;
-//   5. the thread that owns the winning node commits the collapsed usage
-//      (CollapseInitContainerUsage + AddPod's effect on the next usage rebuild) and
-//      writes the decision record.  Ownership of a node is static, so the commit is
-//      only ever read back by the thread that wrote it: no second barrier.
-// A decision therefore sees every earlier commit, exactly like the reference's
-// sequential Filter calls, and costs one barrier instead of a kernel launch.
+// hs_decide_kernel is ONE persistent cooperative kernel that runs a whole stream of scheduling
+// ops in order.  Per FILTER op (reference: Scheduler.Filter, pkg/scheduler/scheduler.go:1067-1154):
+//   1. the op's 160 B request record is staged in shared memory (cp.async prefetch of the next op
+//      overlaps the current one);
+//   2. every node is evaluated by the quarter warp that owns it — one lane per device slot, the
+//      inventory held in registers (hs_fast.cuh) — or, for the uncommon request shapes, by one
+//      thread running the general evaluator (hs_eval.cuh).  When the cluster is larger than the
+//      resident lanes, owners stream their nodes from the SoA inventory with coalesced 128-bit loads;
+//   3. warp-shuffle + shared-memory arg-best, then ONE 16-byte L2 slot per op carries both the
+//      atomicMax of the packed (score, position) key and the grid barrier's arrival count;
+//   4. the owner of the winning node commits the collapsed usage (CollapseInitContainerUsage +
+//      AddPod's effect on the next usage rebuild) and writes the decision record.  Ownership of a
+//      node is static, so a commit is only ever read back by the lanes that wrote it: no second
+//      barrier, and the next op's sweep starts immediately everywhere else.
+// A decision therefore sees every earlier commit, exactly like the reference's sequential Filter
+// calls, and costs one barrier instead of a kernel launch.
 //
-// Integer/compare work on CUDA cores: there is no dense contraction on this path,
-// so no tensor cores.
+// Integer/compare work on CUDA cores: there is no dense contraction on this path, so no tensor
+// cores.
 #include <cuda_runtime.h>
 
 #include "hs_eval.cuh"
 #include "hs_fast.cuh"
 
-
-
+// Inventory layout (node-major structure-of-arrays): dyn[node*8 + slot] = {used, usedmem, usedcores,
+// dflags}, stat[node*8 + slot] = {count, totalmem, totalcore, packed}.  The 8 lanes of a node read
+// 128 contiguous bytes of each array, a warp (4 nodes) 512 B: fully coalesced 128-bit loads.
 __device__ __forceinline__ void load_node(const KernelArgs& ka, int node, uint32_t nflags, NodeWork& w) {
-  const int tile = node / HS_TILE, lane = node % HS_TILE;
-  const int4* dy = ka.dyn + (size_t)tile * HS_D * HS_TILE + lane;
-  const int4* st = ka.stat + (size_t)tile * HS_D * HS_TILE + lane;
+  const int4* dy = ka.dyn + (size_t)node * HS_D;
+  const int4* st = ka.stat + (size_t)node * HS_D;
   int4 a[HS_D], b[HS_D];
 #pragma unroll
-  for (int d = 0; d < HS_D; d++) { a[d] = dy[d * HS_TILE]; b[d] = __ldg(st + d * HS_TILE); }
+  for (int d = 0; d < HS_D; d++) { a[d] = dy[d]; b[d] = __ldg(st + d); }
 #pragma unroll
   for (int d = 0; d < HS_D; d++) {
     w.used[d] = a[d].x; w.mem[d] = a[d].y; w.cores[d] = a[d].z; w.dflags[d] = (uint32_t)a[d].w;
@@ -42,14 +42,11 @@ __device__ __forceinline__ void load_node(const KernelArgs& ka, int node, uint32
   w.order = 0x76543210u;
 }
 
-__device__ __forceinline__ void reload_usage(const KernelArgs& ka, int node, NodeWork& w) {
-  const int tile = node / HS_TILE, lane = node % HS_TILE;
-  const int4* dy = ka.dyn + (size_t)tile * HS_D * HS_TILE + lane;
-#pragma unroll
-  for (int d = 0; d < HS_D; d++) {
-    const int4 a = dy[d * HS_TILE];
-    w.used[d] = a.x; w.mem[d] = a.y; w.cores[d] = a.z;
-  }
+__device__ __forceinline__ void load_dev(const KernelArgs& ka, int node, int slot, DevRegs& n) {
+  const int4 a = ka.dyn[(size_t)node * HS_D + slot];
+  const int4 b = __ldg(ka.stat + (size_t)node * HS_D + slot);
+  n.used = a.x; n.mem = a.y; n.cores = a.z; n.dflags = (uint32_t)a.w;
+  n.count = b.x; n.totmem = b.y; n.totcore = b.z; n.packed = (uint32_t)b.w;
 }
 
 // CollapseInitContainerUsage (pkg/device/initContainer.go:36-114) folded into the usage
@@ -85,13 +82,12 @@ __device__ void collapse_rows(const DevEntry* ent, const DevAlloc* al, uint32_t 
 }
 
 __device__ __forceinline__ void store_usage(const KernelArgs& ka, int node, const int4* delta, int sign) {
-  const int tile = node / HS_TILE, lane = node % HS_TILE;
-  int4* dy = ka.dyn + (size_t)tile * HS_D * HS_TILE + lane;
+  int4* dy = ka.dyn + (size_t)node * HS_D;
   for (int d = 0; d < HS_D; d++) {
     if (delta[d].x == 0 && delta[d].y == 0 && delta[d].z == 0) continue;
-    int4 v = dy[d * HS_TILE];
+    int4 v = dy[d];
     v.x += sign * delta[d].x; v.y += sign * delta[d].y; v.z += sign * delta[d].z;
-    dy[d * HS_TILE] = v;
+    dy[d] = v;
   }
 }
 
@@ -114,28 +110,25 @@ __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
   f.c0 = c0; f.c1 = c1; f.pad = 0;
 }
 
-// ---- grid-wide barrier ---------------------------------------------------------------------------
-// One arrival counter in L2, never reset inside a launch: barrier k completes when it reaches
-// (k+1) * gridDim.x.  The launch is cooperative, so every CTA is resident.  Thread 0 publishes this
-// CTA's arg-best (atomicMax) before its release-add, polls with relaxed loads (no L1 invalidation
-// inside the spin), then performs one acquire load.
-__device__ __forceinline__ void grid_barrier(uint32_t* arrive, uint32_t expected) {
-  __syncthreads();
+// Arg-best + grid barrier in one 16-byte L2 slot per op: {best key, arrivals}.  Thread 0 of every CTA
+// folds its CTA's key in with atomicMax, then release-adds its arrival; it polls the slot with one
+// 128-bit relaxed load, so the value that ends the spin already carries the winner — no second
+// round trip and no L1 invalidation inside the spin.  Both words live in one L2 sector and every
+// CTA's max is ordered before its arrival, so arrivals == gridDim.x implies the key is final.  The
+// launch is cooperative, so every CTA is resident.  Returns the winning key to the whole CTA.
+__device__ __forceinline__ unsigned long long argbest_barrier(OpSync* slot, unsigned long long cta_key,
+                                                              unsigned long long* s_win) {
   if (threadIdx.x == 0) {
-    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(arrive) : "memory");
-    uint32_t v;
+    if (cta_key) atomicMax(&slot->best, cta_key);
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
+    unsigned long long best, cnt;
     do {
-      asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(arrive) : "memory");
-    } while (v < expected);
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(arrive) : "memory");
+      asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
+    } while ((uint32_t)cnt < gridDim.x);
+    *s_win = best;
   }
   __syncthreads();
-}
-
-__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
+  return *s_win;
 }
 
 // ---- request staging: the next op's 160 B record is prefetched with cp.async while the current
@@ -150,60 +143,48 @@ __device__ __forceinline__ void prefetch_op(const DevPod* src, DevPod* dst) {
 }
 __device__ __forceinline__ void prefetch_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-__device__ __forceinline__ void load_regs(const KernelArgs& ka, int node, NodeRegs& n) {
-  const int tile = node / HS_TILE, lane = node % HS_TILE;
-  const int4* dy = ka.dyn + (size_t)tile * HS_D * HS_TILE + lane;
-  const int4* st = ka.stat + (size_t)tile * HS_D * HS_TILE + lane;
-  int4 a[HS_D], b[HS_D];
-#pragma unroll
-  for (int d = 0; d < HS_D; d++) { a[d] = dy[d * HS_TILE]; b[d] = __ldg(st + d * HS_TILE); }
-#pragma unroll
-  for (int d = 0; d < HS_D; d++) {
-    n.used[d] = a[d].x; n.mem[d] = a[d].y; n.cores[d] = a[d].z; n.dflags[d] = (uint32_t)a[d].w;
-    n.count[d] = b[d].x; n.totmem[d] = b[d].y; n.totcore[d] = b[d].z; n.packed[d] = (uint32_t)b[d].w;
-  }
-}
 
-__device__ __forceinline__ void regs_to_work(const NodeRegs& n, uint32_t nflags, NodeWork& w) {
-#pragma unroll
-  for (int d = 0; d < HS_D; d++) {
-    w.used[d] = n.used[d]; w.mem[d] = n.mem[d]; w.cores[d] = n.cores[d]; w.dflags[d] = n.dflags[d];
-    w.count[d] = n.count[d]; w.totmem[d] = n.totmem[d]; w.totcore[d] = n.totcore[d]; w.packed[d] = n.packed[d];
-  }
-  w.ndev = NF_NDEV(nflags);
-  w.order = 0x76543210u;
-}
+#define FULL 0xffffffffu
 
-extern "C" __global__ void __launch_bounds__(128, 1)
+extern "C" __global__ void __launch_bounds__(512, 1)
 hs_decide_kernel(const KernelArgs ka) {
   __shared__ __align__(16) DevPod s_op[2];
   __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
-  __shared__ unsigned long long s_red[4];
+  __shared__ unsigned long long s_red[16];
+  __shared__ unsigned long long s_win;
 
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int gsize = gridDim.x * blockDim.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const bool resident = ka.n_nodes <= gsize;  // every thread owns at most one node: it stays in registers
+  const int glane = lane & 7;                 // device slot owned by this lane
+  const int gbase = lane & 24;                // first lane of this node's quarter warp
+  const uint32_t gmask = 0xffu << gbase;
+  const int gg = gtid >> 3;                   // node-owner group id
+  const int ngroups = (gridDim.x * blockDim.x) >> 3;
+  const bool resident = ka.n_nodes <= ngroups;  // every group owns at most one node: it stays in registers
 
-  NodeRegs reg;                // the owned node (resident mode): usage kept current by this thread's own commits
+  DevRegs D;                   // the owned device (resident mode), kept current by this group's own commits
+  D.used = D.mem = D.cores = D.count = D.totmem = D.totcore = 0;
+  D.packed = D.dflags = 0;
   uint32_t my_flags = 0;
   int my_pos = -1;
-#pragma unroll
-  for (int d = 0; d < HS_D; d++) {
-    reg.used[d] = reg.mem[d] = reg.cores[d] = reg.count[d] = reg.totmem[d] = reg.totcore[d] = 0;
-    reg.packed[d] = reg.dflags[d] = 0;
+  if (resident && gg < ka.n_nodes) {
+    my_flags = ka.node_flags[gg];
+    load_dev(ka, gg, glane, D);
+    if (my_flags & NF_ALIVE) my_pos = ka.cand_pos ? ka.cand_pos[gg] : gg;
   }
-  if (resident && gtid < ka.n_nodes) {
-    my_flags = ka.node_flags[gtid];
-    load_regs(ka, gtid, reg);
-    if (my_flags & NF_ALIVE) my_pos = ka.cand_pos ? ka.cand_pos[gtid] : gtid;
-  }
+  // ComputeDefaultScore of the owned node only changes when its group commits/releases on it: cached
+  float my_pre = fast_node_score(D);
+  bool dirty = false;          // usage of the owned node changed: refresh my_pre at the next convergent point
+  bool reload = false;         // the general path committed through global memory: re-read the slot
 
-  DevAlloc la[HS_MAX_ALLOC];   // general path: picks of this thread's best node for the current op
+  DevAlloc la[HS_MAX_ALLOC];   // general path (lane 0 of the group): picks of the best owned node for the current op
   uint32_t fail_count = 0;     // no-fit decisions so far: identical in every thread
-  uint32_t barriers = 0;       // grid barriers executed in this launch: identical in every thread
   int r = ka.op_begin;
   if (r < ka.n_ops) prefetch_op(ka.pods + r, &s_op[0]);
+
+  const bool timing = ka.timing != nullptr && gtid == 0;   // diagnostic phase clocks (HS_TIMING=1), block 0 only
+  long long tc = timing ? clock64() : 0;
+#define TICK(slot) do { if (timing) { const long long t_ = clock64(); ka.timing[slot] += (unsigned long long)(t_ - tc); tc = t_; } } while (0)
 
   for (; r < ka.n_ops; r++) {
     const int buf = (r - ka.op_begin) & 1;
@@ -211,29 +192,39 @@ hs_decide_kernel(const KernelArgs ka) {
     __syncthreads();             // op r is staged; every thread is done with the other buffer and with s_ent
     if (r + 1 < ka.n_ops) prefetch_op(ka.pods + r + 1, &s_op[buf ^ 1]);
     const DevPod& pod = s_op[buf];
+    if (resident && __any_sync(FULL, dirty || reload)) {   // warp-uniform: refresh what a commit/release changed
+      if (reload && gg < ka.n_nodes) load_dev(ka, gg, glane, D);
+      my_pre = fast_node_score(D);
+      dirty = false; reload = false;
+    }
+    TICK(0);
 
     if (pod.op == OP_RELEASE) {
       // podManager.DelPod + usage release (scheduler.go:226-253): the owner subtracts what the commit added.
-      // An in-batch reference is only trusted by the thread that wrote that decision (its own stores).
+      // An in-batch reference is resolved by each group's lane 0; only the group that wrote that decision is
+      // guaranteed to see it, and only that group can match the ownership test.
       int node = pod.rel_node;
       const int4* rows;
       if (node >= 0) rows = ka.rel_pool + pod.rel_off;
       else {
         node = ka.decisions[pod.rel_ref].node;
-        rows = ka.commit_delta + (size_t)pod.rel_ref * HS_D;
         if (ka.decisions[pod.rel_ref].status != 0) node = -1;
+        node = __shfl_sync(FULL, node, gbase);
+        rows = ka.commit_delta + (size_t)pod.rel_ref * HS_D;
       }
-      if (node >= 0 && node < ka.n_nodes && (node % gsize) == gtid) {
-        int4 delta[HS_D];
-#pragma unroll
-        for (int d = 0; d < HS_D; d++) delta[d] = rows[d];
-        store_usage(ka, node, delta, -1);
-        if (resident) {
-#pragma unroll
-          for (int d = 0; d < HS_D; d++) { reg.used[d] -= delta[d].x; reg.mem[d] -= delta[d].y; reg.cores[d] -= delta[d].z; }
+      if (node >= 0 && node < ka.n_nodes && (node % ngroups) == gg) {
+        const int4 delta = rows[glane];
+        if (delta.x | delta.y | delta.z) {
+          int4* p = ka.dyn + (size_t)node * HS_D + glane;
+          int4 v = *p;
+          v.x -= delta.x; v.y -= delta.y; v.z -= delta.z;
+          *p = v;
+          if (resident) { D.used -= delta.x; D.mem -= delta.y; D.cores -= delta.z; }
         }
+        dirty = true;
       }
       if (gtid == 0) { ka.decisions[r].status = 2; ka.decisions[r].n_alloc = 0; }
+      TICK(1);
       continue;
     }
     if (pod.op != OP_FILTER) {
@@ -252,52 +243,43 @@ hs_decide_kernel(const KernelArgs ka) {
       ent = s_ent;
     }
 
-    // ---- sweep: evaluate owned nodes --------------------------------------------------------
-    unsigned long long my_key = 0;
+    // ---- sweep: every group evaluates the node(s) it owns --------------------------------------
+    unsigned long long my_key = 0;   // same value in all 8 lanes of a group
     int my_node = -1;
     float my_score = 0.0f;
     uint32_t my_nalloc = 0;
     FastEval fe;
-    fe.cand = 0; fe.qpos = 0; fe.cores = 0;
+    fe.cand = 0; fe.q = 0; fe.slot_of = 0; fe.memreq = 0; fe.cores = 0;
     if (fast) {
       if (resident) {
-        if (my_pos >= 0 && fast_fit(reg, (uint32_t)gtid, my_flags, pod, pod.e0, ka, fe)) {
-          my_score = fast_node_score(reg);
+        const bool fit = fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);   // whole warp, collectives inside
+        if (fit && my_pos >= 0) {
+          my_score = my_pre;
           my_key = make_key(my_score, spread, (uint32_t)(ka.pos_base + my_pos));
-          my_node = gtid;
+          my_node = gg;
         }
       } else {
-        NodeRegs n;
+        DevRegs n;
         FastEval f2;
-        for (int node = gtid; node < ka.n_nodes; node += gsize) {
+        for (int node = gg; node < ka.n_nodes; node += ngroups) {   // n_nodes % 32 == 0: warp-uniform trip count
           const uint32_t nf = ka.node_flags[node];
-          if (!(nf & NF_ALIVE)) continue;
-          const int pos = ka.cand_pos ? ka.cand_pos[node] : node;
-          if (pos < 0) continue;
-          load_regs(ka, node, n);
-          if (fast_fit(n, (uint32_t)node, nf, pod, pod.e0, ka, f2)) {
-            const float sc = fast_node_score(n);
+          const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
+          load_dev(ka, node, glane, n);
+          const bool fit = fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, f2);
+          const float sc = fast_node_score(n);
+          if (fit && pos >= 0) {
             const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
             if (key > my_key) { my_key = key; my_node = node; my_score = sc; }
           }
         }
       }
     } else {
-      NodeWork w;
-      EvalOut out;
-      if (resident) {
-        if (my_pos >= 0) {
-          regs_to_work(reg, my_flags, w);
-          out.allocs = la; out.n_alloc = 0;
-          float sc;
-          if (dev_score_node<EV_RECORD>(w, pod, ent, (uint32_t)gtid, my_flags, ka, out, &sc)) {
-            my_key = make_key(sc, spread, (uint32_t)(ka.pos_base + my_pos));
-            my_node = gtid; my_score = sc; my_nalloc = out.n_alloc;
-          }
-        }
-      } else {
+      // general evaluator: one thread (lane 0 of the group) per node
+      if (glane == 0) {
+        NodeWork w;
+        EvalOut out;
         DevAlloc tmp[HS_MAX_ALLOC];
-        for (int node = gtid; node < ka.n_nodes; node += gsize) {
+        for (int node = gg; node < ka.n_nodes; node += ngroups) {
           const uint32_t nf = ka.node_flags[node];
           if (!(nf & NF_ALIVE)) continue;
           const int pos = ka.cand_pos ? ka.cand_pos[node] : node;
@@ -314,7 +296,10 @@ hs_decide_kernel(const KernelArgs ka) {
           }
         }
       }
+      my_key = __shfl_sync(FULL, my_key, gbase);
+      my_node = __shfl_sync(FULL, my_node, gbase);
     }
+    TICK(2);
 
     // ---- arg-best: warp shuffle, one atomicMax per CTA, ONE grid barrier -----------------------
     unsigned long long bk = warp_max_u64(my_key);
@@ -324,72 +309,86 @@ hs_decide_kernel(const KernelArgs ka) {
       if (threadIdx.x == 0)
         for (int i = 1; i < (int)(blockDim.x >> 5); i++) bk = s_red[i] > bk ? s_red[i] : bk;
     }
-    if (threadIdx.x == 0 && bk) atomicMax(ka.best + r, bk);
-    barriers++;
-    grid_barrier(ka.counters + 3, barriers * gridDim.x);
-    const unsigned long long win = ld_relaxed_u64(ka.best + r);
+    TICK(3);
+    const unsigned long long win = argbest_barrier(ka.sync + r, bk, &s_win);
+    TICK(4);
 
     if (win != 0) {
-      if (my_key == win) {
-        // ---- commit (owner only) -----------------------------------------------------------
-        int4 delta[HS_D];
-        if (fast) {
-          const uint32_t nf = resident ? my_flags : ka.node_flags[my_node];
-          if (!resident) {   // streaming mode: re-derive the winner's picks (reg is free in this mode)
-            load_regs(ka, my_node, reg);
-            fast_fit(reg, (uint32_t)my_node, nf, pod, pod.e0, ka, fe);
+      const bool mine = my_key == win;   // uniform within the group
+      if (fast) {
+        if (!resident && __any_sync(FULL, mine)) {
+          // streaming mode: re-derive the winner's evaluation (collectives → the whole warp takes part)
+          const int node = my_node >= 0 ? my_node : 0;
+          const uint32_t nf = ka.node_flags[node];
+          load_dev(ka, node, glane, D);
+          fast_fit(D, glane, (uint32_t)node, nf, pod, pod.e0, ka, fe);
+          my_flags = nf;
+        }
+        if (mine) {
+          // ---- commit: each lane of the winning group commits its own device ------------------
+          int my_row;
+          const int np = fast_pick(glane, (uint32_t)my_node, my_flags, pod, pod.e0, ka, fe, &my_row);
+          uint32_t off = 0;
+          if (glane == 0) off = atomicAdd(ka.counters + 0, (uint32_t)np);
+          off = __shfl_sync(gmask, off, gbase);
+          int4 delta = make_int4(0, 0, 0, 0);
+          if (my_row >= 0) {
+            delta = make_int4(1, fe.memreq, fe.cores, 0);
+            DevAlloc a;
+            a.entry = 0; a.dev = (uint8_t)glane; a.usedcores = (int16_t)fe.cores; a.usedmem = fe.memreq;
+            if (off + (uint32_t)my_row < ka.alloc_cap) ka.allocs[off + my_row] = a;
+            int4* p = ka.dyn + (size_t)my_node * HS_D + glane;
+            int4 v = *p;
+            v.x += 1; v.y += fe.memreq; v.z += fe.cores;
+            *p = v;
+            if (resident) { D.used += 1; D.mem += fe.memreq; D.cores += fe.cores; }
           }
-          int picks[HS_D];
-          const int np = fast_pick((uint32_t)my_node, nf, pod, pod.e0, ka, fe, picks);
-          my_nalloc = (uint32_t)np;
-#pragma unroll
-          for (int d = 0; d < HS_D; d++) delta[d] = make_int4(0, 0, 0, 0);
-          for (int i = 0; i < np; i++) {
-            const int s = picks[i];
-            int memreq = 0;
-#pragma unroll
-            for (int d = 0; d < HS_D; d++) if (d == s) memreq = fe.memreq[d];
-            la[i].entry = 0; la[i].dev = (uint8_t)s; la[i].usedcores = (int16_t)fe.cores; la[i].usedmem = memreq;
-#pragma unroll
-            for (int d = 0; d < HS_D; d++) if (d == s) delta[d] = make_int4(1, memreq, fe.cores, 0);
+          ka.commit_delta[(size_t)r * HS_D + glane] = delta;
+          if (glane == 0) {
+            DevDecision dec;
+            dec.status = 0; dec.node = my_node; dec.score = my_score; dec.alloc_off = off; dec.n_alloc = (uint32_t)np;
+            dec.fail_slot = 0xffffffffu; dec.pad[0] = dec.pad[1] = 0;
+            ka.decisions[r] = dec;
           }
-        } else {
+          dirty = true;
+        }
+      } else if (mine) {
+        if (glane == 0) {
+          int4 delta[HS_D];
           collapse_rows(ent, la, my_nalloc, delta);
+          const uint32_t off = atomicAdd(ka.counters + 0, my_nalloc);
+          for (uint32_t i = 0; i < my_nalloc && off + i < ka.alloc_cap; i++) ka.allocs[off + i] = la[i];
+          store_usage(ka, my_node, delta, +1);
+          for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)r * HS_D + d] = delta[d];
+          DevDecision dec;
+          dec.status = 0; dec.node = my_node; dec.score = my_score; dec.alloc_off = off; dec.n_alloc = my_nalloc;
+          dec.fail_slot = 0xffffffffu; dec.pad[0] = dec.pad[1] = 0;
+          ka.decisions[r] = dec;
         }
-        const uint32_t off = atomicAdd(ka.counters + 0, my_nalloc);
-        for (uint32_t i = 0; i < my_nalloc && off + i < ka.alloc_cap; i++) ka.allocs[off + i] = la[i];
-        store_usage(ka, my_node, delta, +1);
-        if (resident) {
-#pragma unroll
-          for (int d = 0; d < HS_D; d++) { reg.used[d] += delta[d].x; reg.mem[d] += delta[d].y; reg.cores[d] += delta[d].z; }
-        }
-#pragma unroll
-        for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)r * HS_D + d] = delta[d];
-        DevDecision dec;
-        dec.status = 0; dec.node = my_node; dec.score = my_score; dec.alloc_off = off; dec.n_alloc = my_nalloc;
-        dec.fail_slot = 0xffffffffu; dec.pad[0] = dec.pad[1] = 0;
-        ka.decisions[r] = dec;
+        __syncwarp(gmask);       // lane 0's stores to the slot rows precede the group's reload
+        reload = true;
       }
     } else {
       // ---- no node fits: per-node reasons for FailedNodes (scheduler.go:1109-1114) ------------
       if (fail_count >= ka.fail_cap) break;  // fail buffer full: the host drains it and resumes at op r
-      DevFail* fb = ka.fail + (size_t)fail_count * ka.n_nodes;
-      NodeWork w;
-      EvalOut out;
-      for (int node = gtid; node < ka.n_nodes; node += gsize) {
-        const uint32_t nf = ka.node_flags[node];
-        DevFail f;
-        f.kind_cards = FK_NOT_CANDIDATE; f.c0 = f.c1 = f.pad = 0;
-        const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
-        if (pos >= 0) {
-          if (resident) regs_to_work(reg, nf, w);
-          else load_node(ka, node, nf, w);
-          out.fkind = FK_NONE; out.fcards = 0;
-          float sc;
-          dev_score_node<EV_EXPLAIN>(w, pod, ent, (uint32_t)node, nf, ka, out, &sc);
-          pack_fail(out, f);
+      if (glane == 0) {
+        DevFail* fb = ka.fail + (size_t)fail_count * ka.n_nodes;
+        NodeWork w;
+        EvalOut out;
+        for (int node = gg; node < ka.n_nodes; node += ngroups) {
+          const uint32_t nf = ka.node_flags[node];
+          DevFail f;
+          f.kind_cards = FK_NOT_CANDIDATE; f.c0 = f.c1 = f.pad = 0;
+          const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
+          if (pos >= 0) {
+            load_node(ka, node, nf, w);
+            out.fkind = FK_NONE; out.fcards = 0;
+            float sc;
+            dev_score_node<EV_EXPLAIN>(w, pod, ent, (uint32_t)node, nf, ka, out, &sc);
+            pack_fail(out, f);
+          }
+          fb[node] = f;
         }
-        fb[node] = f;
       }
       if (gtid == 0) {
         DevDecision dec;
@@ -399,6 +398,7 @@ hs_decide_kernel(const KernelArgs ka) {
       }
       fail_count++;
     }
+    TICK(6);
   }
   prefetch_wait();
   if (gtid == 0) { ka.counters[2] = (uint32_t)r; ka.counters[1] = fail_count; }
@@ -448,7 +448,7 @@ hs_sweep_kernel(const KernelArgs ka, int op) {
   __syncthreads();
   if (threadIdx.x == 0) {
     for (int i = 1; i < (int)(blockDim.x >> 5); i++) bk = s_red[i] > bk ? s_red[i] : bk;
-    if (bk) atomicMax(ka.best + op, bk);
+    if (bk) atomicMax(&ka.sync[op].best, bk);
   }
 }
 
@@ -498,6 +498,39 @@ hs_commit_kernel(const KernelArgs ka, int op, unsigned long long win) {
     }
   }
   ka.decisions[op] = dec;
+}
+
+// Self-check of the branch-free divide (hs_fast.cuh) against the IEEE divide, over the operand space the
+// path produces: numerators/denominators that are int32 counters.  Counts mismatching bit patterns.
+extern "C" __global__ void hs_divcheck_kernel(unsigned long long n, unsigned long long seed, unsigned long long* bad) {
+  unsigned long long local = 0;
+  for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+       i += (unsigned long long)gridDim.x * blockDim.x) {
+    unsigned long long x = (i + seed) * 0x9E3779B97F4A7C15ull;
+    x ^= x >> 29; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 32;
+    int num, den;
+    if (i < (1ull << 24)) { num = (int)(i & 4095u); den = (int)(i >> 12) + 1; }        // exhaustive small grid
+    else {
+      const int sh_n = (int)((x >> 58) & 31u), sh_d = (int)((x >> 53) & 31u);
+      num = (int)((x & 0x7fffffffu) >> sh_n);
+      den = (int)(((x >> 22) & 0x7fffffffu) >> sh_d);
+      if (den == 0) den = 1;
+    }
+    const float a = idiv_rn(num, den);
+    const float b = __fdiv_rn((float)num, (float)den);
+    if (__float_as_uint(a) != __float_as_uint(b)) local++;
+  }
+  if (local) atomicAdd(bad, local);
+}
+extern "C" long long hs_launch_divcheck(unsigned long long n, unsigned long long seed) {
+  unsigned long long* d = nullptr;
+  unsigned long long hbad = 0;
+  if (cudaMalloc(&d, sizeof *d) != cudaSuccess) return -1;
+  cudaMemset(d, 0, sizeof *d);
+  hs_divcheck_kernel<<<1184, 256>>>(n, seed, d);
+  if (cudaMemcpy(&hbad, d, sizeof hbad, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaFree(d); return -1; }
+  cudaFree(d);
+  return (long long)hbad;
 }
 
 // ---- host-callable launch wrappers (kept here so hs_engine.cu stays plain C++) ---------------

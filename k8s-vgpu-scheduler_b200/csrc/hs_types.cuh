@@ -120,6 +120,13 @@ struct DevFail {            // 16 B
   uint32_t pad;
 };
 
+// one 16 B slot per op: the arg-best key and the grid barrier that publishes it share an L2 sector
+struct OpSync {
+  unsigned long long best;      // packed argbest key (make_key), 0 = no node fits
+  uint32_t arrived;             // CTAs that have folded their key in
+  uint32_t pad;
+};
+
 struct KernelArgs {
   // inventory
   int4* dyn;
@@ -141,10 +148,11 @@ struct KernelArgs {
   DevAlloc* allocs;
   uint32_t alloc_cap;
   int4* commit_delta;           // [op][HS_D] collapsed {slots, mem, cores, 0} of a committed decision
-  unsigned long long* best;     // [op] packed argbest key, zeroed by the host
+  OpSync* sync;                 // [op] {argbest key, CTA arrivals}, zeroed by the host
   DevFail* fail;                // [fail_cap][n_nodes]
   uint32_t fail_cap;
   uint32_t* counters;           // [0] alloc cursor, [1] fail cursor, [2] ops completed, [3] barrier arrive, [4] barrier epoch
   // multi-GPU: global position of this shard's slot 0 (argbest key carries global positions)
   int32_t pos_base;
+  unsigned long long* timing;   // diagnostic: 8 phase-clock accumulators written by block 0 (NULL = off)
 };

@@ -136,3 +136,13 @@ def test_golden_filter_cases_on_gpu():
         ids = [seg.split(",")[0] for ctr in anno.split(";") for seg in ctr.split(":") if "," in seg]
         assert ids and ids[-1] in case["wantPodAnnotationDeviceIDs"], case["name"]
         e.close()
+
+
+def test_branch_free_divide_matches_ieee():
+    # the fast path's float32 divide must equal the IEEE divide bit for bit on int32-counter operands
+    import ctypes as C
+    import k8s_vgpu_scheduler_b200.engine as eng
+    L = eng.lib()
+    L.hs_debug_divcheck.restype = C.c_longlong
+    L.hs_debug_divcheck.argtypes = [C.c_ulonglong, C.c_ulonglong]
+    assert L.hs_debug_divcheck(1 << 28, 20260601) == 0
