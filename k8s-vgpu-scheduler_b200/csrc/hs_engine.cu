@@ -649,7 +649,7 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
   int block = h->block;
   int maxb = hs_decide_max_blocks(block, h->device);
   if (maxb <= 0) { h->err = "hs_decide_kernel cannot be launched cooperatively on this device"; return HS_ERR_CUDA; }
-  int grid = std::min(maxb, std::max(1, (n_nodes * HS_D + block - 1) / block));   // 8 lanes per node when it fits
+  int grid = std::min(std::min(maxb, 1024), std::max(1, (n_nodes * HS_D + block - 1) / block));   // 8 lanes per node when it fits
 
   h->fail_host.clear();
   h->op_fail_slot.assign(n_ops, 0xffffffffu);
@@ -1018,7 +1018,7 @@ void hs_destroy(hs_handle* h) {
   if (h->d_dyn) { cudaFree(h->d_dyn); cudaFree(h->d_stat); cudaFree(h->d_flags); cudaFree(h->d_pair); }
   h->b_pods.release(); h->b_entries.release(); h->b_uuid.release(); h->b_rel.release(); h->b_dec.release();
   h->b_alloc.release(); h->b_delta.release(); h->b_best.release(); h->b_fail.release(); h->b_counters.release();
-  h->b_candpos.release();
+  h->b_candpos.release(); h->b_timing.release();
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->stream) cudaStreamDestroy(h->stream);

@@ -450,14 +450,16 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   return true;
 }
 
-// Order-preserving key: best node == max key.  hi 32 bits: float32 score mapped to
-// an unsigned that sorts like the float (inverted for node policy "spread", which picks
-// the MIN score, node_policy.go:48-54); lo 32 bits: candidate position + 1, so among
-// equal scores the highest position wins (canonical rule 3) and 0 means "no node".
+// Order-preserving key: best node == max key.  Bits 63-32: float32 score mapped to an unsigned that
+// sorts like the float (inverted for node policy "spread", which picks the MIN score,
+// node_policy.go:48-54); bits 31-8: candidate position + 1, so among equal scores the highest position
+// wins (canonical rule 3) and 0 means "no node"; bits 7-0: reserved for the barrier epoch tag.
+#define KEY_POS(k) ((int)(((k) >> 8) & 0xffffffull) - 1)
+#define KEY_VALID(k) ((((k) >> 8) & 0xffffffull) != 0)
 __device__ __forceinline__ unsigned long long make_key(float score, bool spread, uint32_t pos) {
   if (score == 0.0f) score = 0.0f;  // -0 == +0 in Go's comparison
   uint32_t u = __float_as_uint(score);
   u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
   if (spread) u = ~u;
-  return ((unsigned long long)u << 32) | (unsigned long long)(pos + 1u);
+  return ((unsigned long long)u << 32) | ((unsigned long long)((pos + 1u) & 0xffffffu) << 8);
 }

@@ -110,22 +110,32 @@ __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
   f.c0 = c0; f.c1 = c1; f.pad = 0;
 }
 
-// Arg-best + grid barrier in one 16-byte L2 slot per op: {best key, arrivals}.  Thread 0 of every CTA
-// folds its CTA's key in with atomicMax, then release-adds its arrival; it polls the slot with one
-// 128-bit relaxed load, so the value that ends the spin already carries the winner — no second
-// round trip and no L1 invalidation inside the spin.  Both words live in one L2 sector and every
-// CTA's max is ordered before its arrival, so arrivals == gridDim.x implies the key is final.  The
-// launch is cooperative, so every CTA is resident.  Returns the winning key to the whole CTA.
-__device__ __forceinline__ unsigned long long argbest_barrier(OpSync* slot, unsigned long long cta_key,
-                                                              unsigned long long* s_win) {
-  if (threadIdx.x == 0) {
-    if (cta_key) atomicMax(&slot->best, cta_key);
-    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
-    unsigned long long best, cnt;
-    do {
-      asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
-    } while ((uint32_t)cnt < gridDim.x);
-    *s_win = best;
+// Arg-best + grid barrier in one 16-byte L2 slot per op: {best key, arrivals}.  Warp 0 of every CTA
+// max-reduces the CTA's warp keys with shuffles; its lane 0 folds the result in with atomicMax, then
+// release-adds the CTA's arrival and polls the slot with ONE 128-bit relaxed load per round, so the
+// value that ends the spin already carries the winner (no second round trip, no L1 invalidation in
+// the spin, one poller and one polled sector per CTA).  Every CTA's max is ordered before its arrival
+// by the release, and both words share an L2 sector, so arrivals == gridDim.x implies the key is
+// final.  The launch is cooperative, so every CTA is resident.  Returns the winning key to the CTA.
+// (An all-to-all ring of per-CTA slots polled by a whole warp was measured slower: 157 pollers x 5
+// lines per round hot-spot the L2 slices and delay the arrivals themselves.)
+__device__ __forceinline__ unsigned long long slot_argbest(OpSync* slot, unsigned long long warp_key,
+                                                           unsigned long long* s_red, unsigned long long* s_win) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  if (lane == 0) s_red[warp] = warp_key;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned long long v = lane < nwarps ? s_red[lane] : 0ull;
+    v = warp_max_u64(v);
+    if (lane == 0) {
+      if (v) atomicMax(&slot->best, v);
+      asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
+      unsigned long long best, cnt;
+      do {
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
+      } while ((uint32_t)cnt < gridDim.x);
+      *s_win = best;
+    }
   }
   __syncthreads();
   return *s_win;
@@ -150,7 +160,7 @@ extern "C" __global__ void __launch_bounds__(512, 1)
 hs_decide_kernel(const KernelArgs ka) {
   __shared__ __align__(16) DevPod s_op[2];
   __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
-  __shared__ unsigned long long s_red[16];
+  __shared__ unsigned long long s_red[32];
   __shared__ unsigned long long s_win;
 
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -302,18 +312,12 @@ hs_decide_kernel(const KernelArgs ka) {
     TICK(2);
 
     // ---- arg-best: warp shuffle, one atomicMax per CTA, ONE grid barrier -----------------------
-    unsigned long long bk = warp_max_u64(my_key);
-    if (blockDim.x > 32) {
-      if (lane == 0) s_red[warp] = bk;
-      __syncthreads();
-      if (threadIdx.x == 0)
-        for (int i = 1; i < (int)(blockDim.x >> 5); i++) bk = s_red[i] > bk ? s_red[i] : bk;
-    }
+    const unsigned long long bk = warp_max_u64(my_key);
     TICK(3);
-    const unsigned long long win = argbest_barrier(ka.sync + r, bk, &s_win);
+    const unsigned long long win = slot_argbest(ka.sync + r, bk, s_red, &s_win);
     TICK(4);
 
-    if (win != 0) {
+    if (KEY_VALID(win)) {
       const bool mine = my_key == win;   // uniform within the group
       if (fast) {
         if (!resident && __any_sync(FULL, mine)) {
@@ -371,7 +375,24 @@ hs_decide_kernel(const KernelArgs ka) {
     } else {
       // ---- no node fits: per-node reasons for FailedNodes (scheduler.go:1109-1114) ------------
       if (fail_count >= ka.fail_cap) break;  // fail buffer full: the host drains it and resumes at op r
-      if (glane == 0) {
+      if (fast) {
+        DevFail* fb = ka.fail + (size_t)fail_count * ka.n_nodes;
+        DevFail nc;
+        nc.kind_cards = FK_NOT_CANDIDATE; nc.c0 = nc.c1 = nc.pad = 0;
+        if (resident) {
+          const DevFail f = fast_explain(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka);   // whole warp
+          if (glane == 0 && gg < ka.n_nodes) fb[gg] = my_pos >= 0 ? f : nc;
+        } else {
+          DevRegs n;
+          for (int node = gg; node < ka.n_nodes; node += ngroups) {   // warp-uniform trip count
+            const uint32_t nf = ka.node_flags[node];
+            const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
+            load_dev(ka, node, glane, n);
+            const DevFail f = fast_explain(n, glane, (uint32_t)node, nf, pod, pod.e0, ka);
+            if (glane == 0) fb[node] = pos >= 0 ? f : nc;
+          }
+        }
+      } else if (glane == 0) {
         DevFail* fb = ka.fail + (size_t)fail_count * ka.n_nodes;
         NodeWork w;
         EvalOut out;
@@ -472,7 +493,7 @@ hs_commit_kernel(const KernelArgs ka, int op, unsigned long long win) {
   }
   __syncthreads();
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  const int pos = (int)((win & 0xffffffffull) - 1ull) - ka.pos_base;
+  const int pos = KEY_POS(win) - ka.pos_base;
   int node = -1;
   if (!ka.cand_pos) node = pos;
   else for (int n = 0; n < ka.n_nodes; n++) if (ka.cand_pos[n] == pos) { node = n; break; }
