@@ -267,7 +267,8 @@ int32_t hs_batch_get(hs_handle* h, uint32_t i, hs_filter_result* out);
  * digest; also counts fits / no-fits.  The consumer a throughput measurement needs, and the
  * "checksum of checksums" parity property at full size.  Layout of the digest: per op in order,
  * status (4 B LE); fit: node name, score bits (4 B LE), then key\0value\0 per annotation in
- * key order; no fit: node\0reason\0 per candidate in candidate order.                        */
+ * key order; no fit: node\0reason\0 per candidate in candidate order.  digest == NULL: every
+ * result is still materialised (what a caller reading the batch does) but not hashed.          */
 int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint64_t* digest);
 
 /* The reference undoes the commit when the annotation PATCH fails

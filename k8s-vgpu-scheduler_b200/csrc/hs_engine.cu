@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <array>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <deque>
@@ -224,6 +225,7 @@ struct hs_handle {
   DBuf<int32_t> b_candpos;
   DBuf<unsigned long long> b_timing;   // HS_TIMING=1: phase clocks of block 0
   bool timing = false;
+  double host_s[4] = {0, 0, 0, 0};      // diagnostic: cumulative host seconds in compile / device+copies / absorb / summary
   uint32_t fail_cap = 32;
   std::vector<OpMeta> metas;            // per device op
   std::vector<int> user_first_op;       // per caller op: index of its FILTER/RELEASE device op
@@ -243,6 +245,9 @@ struct hs_handle {
   std::vector<hs_alloc_entry> r_entries;
   std::vector<hs_kv> r_annos;
   std::vector<hs_failed_node> r_failed;
+  std::string r_buf;                    // device-list annotation of the last assembled result
+  DevFail last_fail = {0xffffffffu, 0, 0, 0};
+  const std::string* last_fail_str = nullptr;
   std::map<std::array<uint32_t, 3>, std::string> reason_cache;
 
   const char* keep(const std::string& s) { r_strs.push_back(s); return r_strs.back().c_str(); }
@@ -586,7 +591,17 @@ std::string encode_pod_single(const std::vector<std::vector<const hs_alloc_entry
   return res;
 }
 
-const std::string& fail_string(hs_handle* h, const DevFail& f) {
+const std::string& fail_string_slow(hs_handle* h, const DevFail& f);
+inline const std::string& fail_string(hs_handle* h, const DevFail& f) {
+  // neighbouring nodes usually fail for the same reason: one-entry cache in front of the map
+  if (h->last_fail_str && f.kind_cards == h->last_fail.kind_cards && f.c0 == h->last_fail.c0 && f.c1 == h->last_fail.c1)
+    return *h->last_fail_str;
+  const std::string& s = fail_string_slow(h, f);
+  h->last_fail = f;
+  h->last_fail_str = &s;
+  return s;
+}
+const std::string& fail_string_slow(hs_handle* h, const DevFail& f) {
   std::array<uint32_t, 3> key = {f.kind_cards, f.c0, f.c1};
   auto it = h->reason_cache.find(key);
   if (it != h->reason_cache.end()) return it->second;
@@ -674,7 +689,9 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
     if (nfail) {
       size_t base = h->fail_host.size();
       h->fail_host.resize(base + (size_t)nfail * n_nodes);
-      CUDA_OK(h, cudaMemcpy(h->fail_host.data() + base, h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail), cudaMemcpyDeviceToHost));
+      CUDA_OK(h, cudaMemcpyAsync(h->b_fail.h, h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail), cudaMemcpyDeviceToHost, h->stream));
+      CUDA_OK(h, cudaStreamSynchronize(h->stream));
+      memcpy(h->fail_host.data() + base, h->b_fail.h, (size_t)nfail * n_nodes * sizeof(DevFail));
     }
     if (ran == 0 && nfail == 0 && n_ops - done > 0) { h->err = "decide kernel made no progress"; return HS_ERR_CUDA; }
     // decisions of this launch
@@ -726,6 +743,46 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
       int idx = 0;
       for (int i = 0; i < dec.node; i++) if (h->nodes[i].alive) idx++;
       out->node_index = idx;
+    }
+    // Common shape (one container, one NVIDIA/DCU request): the PodDevices bookkeeping below collapses to the
+    // request's type key holding the rows, plus one empty list under every other base type of the node
+    // (score.go:278-282), and the annotation map to four keys.  Same output as the general code, no maps.
+    if (m.n_ctr == 1 && m.n_init == 0 && m.entries.size() == 1 && (m.entries[0].vendor == 0 || m.entries[0].vendor == 1) &&
+        h->b_entries.h[h->b_pods.h[op].entry_off].nums > 0) {
+      const EntryMeta& em = m.entries[0];
+      const VendorInfo& v = h->vendors[em.vendor];
+      bool placed = false;
+      auto put_rows = [&]() {
+        if (dec.n_alloc == 0) { h->r_entries.push_back(hs_alloc_entry{0, em.type.c_str(), nullptr, 0, 0, 0}); return; }
+        for (uint32_t i = 0; i < dec.n_alloc; i++) {
+          const DevAlloc& a = h->b_alloc.h[dec.alloc_off + i];
+          const DevSlot& ds = ns.devs[a.dev];
+          h->r_entries.push_back(hs_alloc_entry{0, em.type.c_str(), ds.uuid.c_str(), (int32_t)ds.index, a.usedmem, (int32_t)a.usedcores});
+        }
+      };
+      for (auto& t : ns.base_types) {
+        if (!placed && em.type <= t) { put_rows(); placed = true; if (em.type == t) continue; }
+        h->r_entries.push_back(hs_alloc_entry{0, t.c_str(), nullptr, 0, 0, 0});
+      }
+      if (!placed) put_rows();
+      std::string& buf = h->r_buf;
+      buf.clear();
+      char num[48];
+      for (uint32_t i = 0; i < dec.n_alloc; i++) {
+        const DevAlloc& a = h->b_alloc.h[dec.alloc_off + i];
+        buf += ns.devs[a.dev].uuid; buf += ','; buf += em.type;
+        snprintf(num, sizeof num, ",%d,%d:", a.usedmem, (int)a.usedcores);
+        buf += num;
+      }
+      buf += ';';
+      // keys in sorted order: "<vendor>-devices-allocated" < "...-to-allocate" < "hami.io/vgpu-node" < "hami.io/vgpu-time"
+      h->r_annos.push_back(hs_kv{v.allocated.c_str(), buf.c_str()});
+      h->r_annos.push_back(hs_kv{v.to_allocate.c_str(), buf.c_str()});
+      h->r_annos.push_back(hs_kv{"hami.io/vgpu-node", ns.name.c_str()});
+      h->r_annos.push_back(hs_kv{"hami.io/vgpu-time", ""});
+      out->entries = h->r_entries.data(); out->n_entries = (uint32_t)h->r_entries.size();
+      out->annotations = h->r_annos.data(); out->n_annotations = (uint32_t)h->r_annos.size();
+      return;
     }
     // per entry: its rows
     std::vector<std::vector<hs_alloc_entry>> rows(m.entries.size());
@@ -907,7 +964,10 @@ void absorb_results(hs_handle* h, int n_ops) {
 
 // Compile caller ops into device ops (implicit release of a pod that is filtered again,
 // scheduler.go:1092-1094), run them, absorb the results.
+static inline double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
 int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
+  const double t0 = now_s();
   std::vector<DevPod> pods;
   std::vector<DevEntry> entries;
   std::vector<uint32_t> uuid_pool;
@@ -951,9 +1011,13 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
   if (!entries.empty()) memcpy(h->b_entries.h, entries.data(), entries.size() * sizeof(DevEntry));
   if (!uuid_pool.empty()) memcpy(h->b_uuid.h, uuid_pool.data(), uuid_pool.size() * sizeof(uint32_t));
   if (!rel.empty()) memcpy(h->b_rel.h, rel.data(), rel.size() * sizeof(int4));
+  const double t1 = now_s();
   int rc = run_device_ops(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap);
   if (rc != HS_OK) return rc;
+  const double t2 = now_s();
   absorb_results(h, n);
+  const double t3 = now_s();
+  h->host_s[0] += t1 - t0; h->host_s[1] += t2 - t1; h->host_s[2] += t3 - t2;
   return HS_OK;
 }
 
@@ -1252,6 +1316,7 @@ static inline void fnv_str(uint64_t& hsh, const char* s) { fnv(hsh, s, strlen(s)
 
 int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint64_t* digest) {
   if (!h) return HS_ERR_INVALID;
+  const double t0 = now_s();
   uint64_t hsh = 1469598103934665603ull;
   uint32_t fit = 0, nofit = 0;
   hs_filter_result r;
@@ -1262,6 +1327,10 @@ int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint6
     else if (h->user_first_op[i] < 0) r.status = HS_ERR_INVALID;
     else assemble_result(h, h->user_first_op[i], &r);
     int32_t st = r.status;
+    if (!digest) {   // materialise only: count, do not hash
+      if (h->user_first_op[i] >= 0 && h->metas[h->user_first_op[i]].kind == OP_FILTER) { if (st == HS_FIT) fit++; else if (st == HS_NOFIT) nofit++; }
+      continue;
+    }
     fnv(hsh, &st, 4);
     if (h->user_first_op[i] >= 0 && h->metas[h->user_first_op[i]].kind != OP_FILTER) continue;
     if (st == HS_FIT) {
@@ -1277,6 +1346,14 @@ int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint6
   if (n_fit) *n_fit = fit;
   if (n_nofit) *n_nofit = nofit;
   if (digest) *digest = hsh;
+  h->host_s[3] += now_s() - t0;
+  return HS_OK;
+}
+
+/* Diagnostic: cumulative host seconds spent in request compile, device run + copies, result absorb, summary. */
+int32_t hs_debug_host_seconds(hs_handle* h, double out[4]) {
+  if (!h) return HS_ERR_INVALID;
+  for (int i = 0; i < 4; i++) out[i] = h->host_s[i];
   return HS_OK;
 }
 

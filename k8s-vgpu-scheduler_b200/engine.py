@@ -144,10 +144,11 @@ class Engine:
     def batch_get_raw(self, i, res):
         return self.L.hs_batch_get(self.h, i, C.byref(res))
 
-    def batch_summary(self):
-        """(n_fit, n_nofit, digest) over every result of the last run_batch."""
+    def batch_summary(self, digest=True):
+        """(n_fit, n_nofit, digest) over every result of the last run_batch; digest=False materialises every
+        result (node, rows, annotation map / FailedNodes) without hashing it."""
         nf, nn, dg = C.c_uint32(), C.c_uint32(), C.c_uint64()
-        self._check(self.L.hs_batch_summary(self.h, C.byref(nf), C.byref(nn), C.byref(dg)))
+        self._check(self.L.hs_batch_summary(self.h, C.byref(nf), C.byref(nn), C.byref(dg) if digest else None))
         return nf.value, nn.value, dg.value
 
     def snapshot(self, node, cap=16):

@@ -38,4 +38,8 @@ print("ops %d filters %d fits %d nofits %d device_ms %.3f  -> %.2f us/op, %.2f u
       (len(part), nfilt, nf, nn, ms, 1e3 * ms / len(part), 1e3 * ms / nfilt))
 for nm, v in zip(names, d):
     print("  %-15s %12d clk  %5.1f%%  %.2f us/decision @1.965GHz" % (nm, v, 100.0 * v / tot, v / 1965.0 / nfilt))
+L.hs_debug_host_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+hs = (C.c_double * 4)()
+L.hs_debug_host_seconds(e.h, hs)
+print('host seconds (cumulative, both batches): compile %.4f device+copies %.4f absorb %.4f summary %.4f  over %d ops' % (hs[0], hs[1], hs[2], hs[3], len(ops)))
 e.close()
