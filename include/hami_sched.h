@@ -279,6 +279,17 @@ int32_t hs_rollback(hs_handle* h, const char* pod_uid);
  * the reference's equivalent is InspectAllNodesUsage, scheduler.go:630-639). */
 int32_t hs_snapshot_node(hs_handle* h, const char* node, hs_device_usage_row* rows, uint32_t cap);
 
+/* ---- measurement / diagnostic hooks (no counterpart in the reference) ----------------------- */
+/* The inventory scan in isolation: compile `pod`, run the sweep-only kernel `iters` times over the
+ * whole inventory (no commit); average device ms per sweep, the winning candidate position, its score. */
+int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* ms_avg, int32_t* node_index, float* score);
+/* Cumulative SM clocks block 0 spent per phase of the decide loop (needs HS_TIMING=1 at hs_create). */
+int32_t hs_debug_timing(hs_handle* h, unsigned long long out[8]);
+/* Cumulative host seconds: request compile, device run + copies, result absorb, summary. */
+int32_t hs_debug_host_seconds(hs_handle* h, double out[4]);
+/* Self-check of the branch-free float32 divide against the IEEE divide on n operand pairs; mismatches. */
+long long hs_debug_divcheck(unsigned long long n, unsigned long long seed);
+
 /* Device time (ms, CUDA events on the engine's stream) and kernel launches of
  * the last hs_filter / hs_run_batch, for bench.py.                          */
 double   hs_last_device_ms(const hs_handle* h);

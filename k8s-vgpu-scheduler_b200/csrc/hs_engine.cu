@@ -24,7 +24,8 @@
 
 extern "C" int hs_launch_decide(const KernelArgs* ka, int grid, int block, cudaStream_t stream);
 extern "C" int hs_decide_max_blocks(int block, int device);
-extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int grid, int block, cudaStream_t stream);
+extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int mode, int grid, int block, cudaStream_t stream);
+extern "C" int hs_sweep_blocks_per_sm(int mode);
 extern "C" int hs_launch_commit(const KernelArgs* ka, int op, unsigned long long win, cudaStream_t stream);
 
 namespace {
@@ -204,6 +205,8 @@ struct hs_handle {
   // inventory mirrors (host) + device arrays
   std::vector<int4> h_dyn, h_stat;
   std::vector<uint32_t> h_flags;
+  std::vector<int4> h_tot;          // per node {flags, sum count, sum totalcore, sum totalmem}: the streamed sweep's node record
+  int4* d_tot = nullptr;
   std::vector<int16_t> h_pair;
   int4* d_dyn = nullptr; int4* d_stat = nullptr; uint32_t* d_flags = nullptr; int16_t* d_pair = nullptr;
   int cap_nodes = 0;       // slots allocated (multiple of HS_TILE)
@@ -324,6 +327,11 @@ int grow_inventory(hs_handle* h, int need_nodes) {
   CUDA_OK(h, cudaMalloc(&ns, (size_t)ncap * HS_D * sizeof(int4)));
   CUDA_OK(h, cudaMalloc(&nf, (size_t)ncap * sizeof(uint32_t)));
   CUDA_OK(h, cudaMalloc(&np, (size_t)ncap * 64 * sizeof(int16_t)));
+  int4* nt = nullptr;
+  CUDA_OK(h, cudaMalloc(&nt, (size_t)ncap * sizeof(int4)));
+  if (h->d_tot) cudaFree(h->d_tot);
+  h->d_tot = nt;
+  h->h_tot.resize((size_t)ncap, make_int4(0, 0, 0, 0));
   if (h->d_dyn) { cudaFree(h->d_dyn); cudaFree(h->d_stat); cudaFree(h->d_flags); cudaFree(h->d_pair); }
   h->d_dyn = nd; h->d_stat = ns; h->d_flags = nf; h->d_pair = np;
   h->h_dyn.resize((size_t)ncap * HS_D, make_int4(0, 0, 0, 0));
@@ -350,6 +358,7 @@ int flush_inventory(hs_handle* h) {
   size_t o = t0 * HS_D * HS_TILE, n = nt * HS_D * HS_TILE;
   CUDA_OK(h, cudaMemcpyAsync(h->d_dyn + o, h->h_dyn.data() + o, n * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
   CUDA_OK(h, cudaMemcpyAsync(h->d_stat + o, h->h_stat.data() + o, n * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, cudaMemcpyAsync(h->d_tot + t0 * HS_TILE, h->h_tot.data() + t0 * HS_TILE, nt * HS_TILE * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
   CUDA_OK(h, cudaMemcpyAsync(h->d_flags + t0 * HS_TILE, h->h_flags.data() + t0 * HS_TILE, nt * HS_TILE * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
   CUDA_OK(h, cudaMemcpyAsync(h->d_pair + t0 * HS_TILE * 64, h->h_pair.data() + t0 * HS_TILE * 64, nt * HS_TILE * 64 * sizeof(int16_t), cudaMemcpyHostToDevice, h->stream));
   CUDA_OK(h, cudaStreamSynchronize(h->stream));  // the pageable host vectors may be resized right after
@@ -627,7 +636,7 @@ const std::string& fail_string_slow(hs_handle* h, const DevFail& f) {
 
 int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_cap) {
   memset(&ka, 0, sizeof ka);
-  ka.dyn = h->d_dyn; ka.stat = h->d_stat; ka.node_flags = h->d_flags; ka.pair = h->d_pair;
+  ka.dyn = h->d_dyn; ka.stat = h->d_stat; ka.node_flags = h->d_flags; ka.node_tot = h->d_tot; ka.pair = h->d_pair;
   ka.n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
   ka.cand_pos = h->have_cand ? h->b_candpos.d : nullptr;
   ka.pods = h->b_pods.d; ka.entries = h->b_entries.d; ka.uuid_pool = h->b_uuid.d; ka.rel_pool = h->b_rel.d;
@@ -1080,6 +1089,7 @@ void hs_destroy(hs_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->d_dyn) { cudaFree(h->d_dyn); cudaFree(h->d_stat); cudaFree(h->d_flags); cudaFree(h->d_pair); }
+  if (h->d_tot) cudaFree(h->d_tot);
   h->b_pods.release(); h->b_entries.release(); h->b_uuid.release(); h->b_rel.release(); h->b_dec.release();
   h->b_alloc.release(); h->b_delta.release(); h->b_best.release(); h->b_fail.release(); h->b_counters.release();
   h->b_candpos.release(); h->b_timing.release();
@@ -1188,6 +1198,11 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
   if (ns.vnpu >= 0) vnpu = ns.vnpu == 1;
   if (vnpu) nf |= NF_VNPU_CORE;
   h->h_flags[slot] = nf;
+  {
+    int4 t = make_int4((int)nf, 0, 0, 0);
+    for (int d = 0; d < n; d++) { t.y += ns.devs[d].count; t.z += ns.devs[d].devcore; t.w += ns.devs[d].devmem; }
+    h->h_tot[slot] = t;
+  }
   mark_dirty(h, slot);
   return HS_OK;
 }
@@ -1208,6 +1223,7 @@ int32_t hs_node_remove(hs_handle* h, const char* name) {
   h->n_alive--;
   h->has_dead = true;
   h->h_flags[slot] = 0;
+  h->h_tot[slot] = make_int4(0, 0, 0, 0);
   for (int d = 0; d < HS_D; d++) { h->h_dyn[inv_idx(slot, d)] = make_int4(0, 0, 0, 0); h->h_stat[inv_idx(slot, d)] = make_int4(0, 0, 0, 0); }
   mark_dirty(h, slot);
   return HS_OK;
@@ -1348,6 +1364,65 @@ int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint6
   if (digest) *digest = hsh;
   h->host_s[3] += now_s() - t0;
   return HS_OK;
+}
+
+/* Measurement hook (no counterpart in the reference): the inventory scan in isolation.  Compiles `pod`, then
+ * runs the sweep-only kernel `iters` times over the whole inventory (no commit) and reports the average
+ * device time per sweep (CUDA events on the engine's stream), the winning position and score.  This is the
+ * kernel whose HBM traffic is N x 256 B per launch. */
+int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* ms_avg, int32_t* node_index, float* score) {
+  if (!h || !pod || iters == 0) return HS_ERR_INVALID;
+  cudaSetDevice(h->device);
+  h->have_cand = false;
+  std::vector<uint32_t> uuid_pool;
+  Compiled c;
+  int rc = compile_pod(h, pod, uuid_pool, c);
+  if (rc != HS_OK) return rc;
+  c.pod.entry_off = 0;
+  if (!h->b_pods.ensure(1) || !h->b_entries.ensure(std::max<size_t>(c.entries.size(), 1)) || !h->b_uuid.ensure(std::max<size_t>(uuid_pool.size(), 1)) ||
+      !h->b_best.ensure(1) || !h->b_counters.ensure(8)) { h->err = "out of memory"; return HS_ERR_CUDA; }
+  h->b_pods.h[0] = c.pod;
+  memcpy(h->b_entries.h, c.entries.data(), c.entries.size() * sizeof(DevEntry));
+  if (!uuid_pool.empty()) memcpy(h->b_uuid.h, uuid_pool.data(), uuid_pool.size() * sizeof(uint32_t));
+  rc = flush_inventory(h);
+  if (rc != HS_OK) return rc;
+  CUDA_OK(h, cudaMemcpyAsync(h->b_pods.d, h->b_pods.h, sizeof(DevPod), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, cudaMemcpyAsync(h->b_entries.d, h->b_entries.h, c.entries.size() * sizeof(DevEntry), cudaMemcpyHostToDevice, h->stream));
+  if (!uuid_pool.empty()) CUDA_OK(h, cudaMemcpyAsync(h->b_uuid.d, h->b_uuid.h, uuid_pool.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, sizeof(OpSync), h->stream));
+  KernelArgs ka;
+  build_kernel_args(h, ka, 1, 0);
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+  const int block = 256;
+  const int mode = !c.pod.fast ? 0 : (((c.pod.flags & PF_NUMA_ASSERT) && c.pod.e0.vendor == HV_NVIDIA) ? 1 : 2);
+  const int grid = std::max(1, std::min(sms * hs_sweep_blocks_per_sm(mode), (ka.n_nodes * HS_D + block - 1) / block));   // one resident wave
+  cudaError_t le = (cudaError_t)hs_launch_sweep(&ka, 0, mode, grid, block, h->stream);   // warm-up
+  if (le != cudaSuccess) { h->err = cudaGetErrorString(le); return HS_ERR_CUDA; }
+  CUDA_OK(h, cudaEventRecord(h->ev0, h->stream));
+  for (uint32_t i = 0; i < iters; i++) {
+    le = (cudaError_t)hs_launch_sweep(&ka, 0, mode, grid, block, h->stream);
+    if (le != cudaSuccess) { h->err = cudaGetErrorString(le); return HS_ERR_CUDA; }
+  }
+  h->launches += iters + 1;
+  CUDA_OK(h, cudaEventRecord(h->ev1, h->stream));
+  CUDA_OK(h, cudaMemcpyAsync(h->b_best.h, h->b_best.d, sizeof(OpSync), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_OK(h, cudaStreamSynchronize(h->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+  if (ms_avg) *ms_avg = (double)ms / iters;
+  const unsigned long long key = h->b_best.h[0].best;
+  const int pos = (int)((key >> 8) & 0xffffffull) - 1;
+  if (node_index) *node_index = pos;
+  if (score) {
+    uint32_t u = (uint32_t)(key >> 32);
+    if (c.pod.flags & PF_NODE_SPREAD) u = ~u;
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+    float f;
+    memcpy(&f, &u, 4);
+    *score = pos >= 0 ? f : 0.0f;
+  }
+  return pos >= 0 ? HS_FIT : HS_NOFIT;
 }
 
 /* Diagnostic: cumulative host seconds spent in request compile, device run + copies, result absorb, summary. */

@@ -244,6 +244,9 @@ hs_decide_kernel(const KernelArgs ka) {
 
     const bool spread = pod.flags & PF_NODE_SPREAD;
     const bool fast = pod.fast != 0;
+    // streaming mode only: in resident mode the full evaluation runs in parallel everywhere, so the winner can
+    // commit straight after the barrier (measured: deferring it to the winner lengthens the critical path)
+    const bool lite = fast && !resident && !((pod.flags & PF_NUMA_ASSERT) && pod.e0.vendor == HV_NVIDIA);
     const DevEntry* ent = &pod.e0;
     if (pod.n_entries > 1) {     // general path with several entries: fetch them from the pool
       const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.entries + pod.entry_off);
@@ -262,7 +265,9 @@ hs_decide_kernel(const KernelArgs ka) {
     fe.cand = 0; fe.q = 0; fe.slot_of = 0; fe.memreq = 0; fe.cores = 0;
     if (fast) {
       if (resident) {
-        const bool fit = fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);   // whole warp, collectives inside
+        // whole warp, collectives inside; without numa-bind the verdict needs no score/sort (fast_fit_lite)
+        const bool fit = lite ? fast_fit_lite(D, glane, gbase, (uint32_t)gg, my_flags, pod, pod.e0, ka)
+                              : fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
         if (fit && my_pos >= 0) {
           my_score = my_pre;
           my_key = make_key(my_score, spread, (uint32_t)(ka.pos_base + my_pos));
@@ -275,9 +280,11 @@ hs_decide_kernel(const KernelArgs ka) {
           const uint32_t nf = ka.node_flags[node];
           const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
           load_dev(ka, node, glane, n);
-          const bool fit = fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, f2);
+          const bool fit = (lite ? fast_fit_lite(n, glane, gbase, (uint32_t)node, nf, pod, pod.e0, ka)
+                                 : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, f2)) && pos >= 0;
+          if (!__any_sync(FULL, fit)) continue;          // warp-uniform: the node score is a quarter-warp collective
           const float sc = fast_node_score(n);
-          if (fit && pos >= 0) {
+          if (fit) {
             const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
             if (key > my_key) { my_key = key; my_node = node; my_score = sc; }
           }
@@ -320,13 +327,15 @@ hs_decide_kernel(const KernelArgs ka) {
     if (KEY_VALID(win)) {
       const bool mine = my_key == win;   // uniform within the group
       if (fast) {
-        if (!resident && __any_sync(FULL, mine)) {
-          // streaming mode: re-derive the winner's evaluation (collectives → the whole warp takes part)
-          const int node = my_node >= 0 ? my_node : 0;
-          const uint32_t nf = ka.node_flags[node];
-          load_dev(ka, node, glane, D);
-          fast_fit(D, glane, (uint32_t)node, nf, pod, pod.e0, ka, fe);
-          my_flags = nf;
+        if ((lite || !resident) && __any_sync(FULL, mine)) {
+          // the sweep only established THAT the node fits (or ran on streamed registers): the winner's warp
+          // now runs the full evaluation to learn which devices (collectives → the whole warp takes part)
+          if (!resident) {
+            const int node = my_node >= 0 ? my_node : 0;
+            my_flags = ka.node_flags[node];
+            load_dev(ka, node, glane, D);
+          }
+          fast_fit(D, glane, (uint32_t)(my_node >= 0 ? my_node : 0), my_flags, pod, pod.e0, ka, fe);
         }
         if (mine) {
           // ---- commit: each lane of the winning group commits its own device ------------------
@@ -425,13 +434,18 @@ hs_decide_kernel(const KernelArgs ka) {
   if (gtid == 0) { ka.counters[2] = (uint32_t)r; ka.counters[1] = fail_count; }
 }
 
-// Sweep-only kernel: evaluates ONE request against the whole inventory and reduces to
-// the arg-best key — no commit.  It is the inventory scan measured for the HBM roofline
-// at inventories larger than L2 and the per-rank step of the sharded path.
-extern "C" __global__ void __launch_bounds__(256)
+// Sweep-only kernel: evaluates ONE request against the whole inventory and reduces to the arg-best key
+// — no commit.  It is the inventory scan measured for the HBM roofline at inventories larger than L2
+//  and the per-rank step of the sharded path.  Common-shape requests stream the node-major
+// SoA with one lane per device: a warp reads 4 nodes = 512 contiguous bytes of each array per step
+// with 128-bit loads, 256 B per node in total.
+// MODE 0: general evaluator (one thread per node); 1: lane-per-device with sort+scan (numa-bind); 2: lane-per-device,
+// order-free verdict.  Separate instantiations keep the streaming kernels' register footprint small.
+template <int MODE>
+__global__ void __launch_bounds__(256, (MODE == 0 ? 2 : (MODE == 1 ? 4 : 6)))
 hs_sweep_kernel(const KernelArgs ka, int op) {
-  __shared__ DevPod s_pod;
-  __shared__ DevEntry s_ent[HS_MAX_E];
+  __shared__ __align__(16) DevPod s_pod;
+  __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
   __shared__ unsigned long long s_red[8];
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.pods + op);
@@ -439,33 +453,59 @@ hs_sweep_kernel(const KernelArgs ka, int op) {
     for (int i = threadIdx.x; i < (int)(sizeof(DevPod) / 4); i += blockDim.x) dst[i] = src[i];
   }
   __syncthreads();
-  {
-    const int ne = s_pod.n_entries;
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.entries + s_pod.entry_off);
+  const DevPod& pod = s_pod;
+  const DevEntry* ent = &s_pod.e0;
+  if (pod.n_entries > 1) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.entries + pod.entry_off);
     uint32_t* dst = reinterpret_cast<uint32_t*>(s_ent);
-    for (int i = threadIdx.x; i < ne * (int)(sizeof(DevEntry) / 4); i += blockDim.x) dst[i] = src[i];
+    for (int i = threadIdx.x; i < pod.n_entries * (int)(sizeof(DevEntry) / 4); i += blockDim.x) dst[i] = src[i];
+    __syncthreads();
+    ent = s_ent;
   }
-  __syncthreads();
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int gsize = gridDim.x * blockDim.x;
-  const bool spread = s_pod.flags & PF_NODE_SPREAD;
+  const int lane = threadIdx.x & 31;
+  const int glane = lane & 7, gbase = lane & 24;
+  const int gg = gtid >> 3;
+  const int ngroups = (gridDim.x * blockDim.x) >> 3;
+  const bool spread = pod.flags & PF_NODE_SPREAD;
   unsigned long long my_key = 0;
-  NodeWork w;
-  EvalOut out;
-  for (int node = gtid; node < ka.n_nodes; node += gsize) {
-    const uint32_t nf = ka.node_flags[node];
-    if (!(nf & NF_ALIVE)) continue;
-    const int pos = ka.cand_pos ? ka.cand_pos[node] : node;
-    if (pos < 0) continue;
-    load_node(ka, node, nf, w);
-    float sc;
-    if (dev_score_node<EV_SCORE>(w, s_pod, s_ent, (uint32_t)node, nf, ka, out, &sc)) {
-      const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
-      my_key = key > my_key ? key : my_key;
+  if (MODE != 0) {
+    constexpr bool lite = MODE == 2;
+    DevRegs n;
+    FastEval fe;
+    const uint32_t gmask = 0xffu << gbase;
+    for (int node = gg; node < ka.n_nodes; node += ngroups) {   // n_nodes % 32 == 0: warp-uniform trip count
+      const int4 nt = __ldg(ka.node_tot + node);                 // {flags, sum count, sum core, sum mem}: one broadcast load
+      const uint32_t nf = (uint32_t)nt.x;
+      const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
+      load_dev(ka, node, glane, n);
+      const bool fit = (lite ? fast_fit_lite(n, glane, gbase, (uint32_t)node, nf, pod, pod.e0, ka)
+                             : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, fe)) && pos >= 0;
+      if (!__any_sync(FULL, fit)) continue;
+      const float sc = fast_node_score_tot(n, gmask, nt.y, nt.z, nt.w);
+      if (fit) {
+        const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
+        my_key = key > my_key ? key : my_key;
+      }
+    }
+  } else if (MODE == 0 && glane == 0) {
+    NodeWork w;
+    EvalOut out;
+    for (int node = gg; node < ka.n_nodes; node += ngroups) {
+      const uint32_t nf = ka.node_flags[node];
+      if (!(nf & NF_ALIVE)) continue;
+      const int pos = ka.cand_pos ? ka.cand_pos[node] : node;
+      if (pos < 0) continue;
+      load_node(ka, node, nf, w);
+      float sc;
+      if (dev_score_node<EV_SCORE>(w, pod, ent, (uint32_t)node, nf, ka, out, &sc)) {
+        const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
+        my_key = key > my_key ? key : my_key;
+      }
     }
   }
   unsigned long long bk = warp_max_u64(my_key);
-  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = bk;
+  if (lane == 0) s_red[threadIdx.x >> 5] = bk;
   __syncthreads();
   if (threadIdx.x == 0) {
     for (int i = 1; i < (int)(blockDim.x >> 5); i++) bk = s_red[i] > bk ? s_red[i] : bk;
@@ -565,10 +605,14 @@ extern "C" int hs_decide_max_blocks(int block, int device) {
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return 0;
   return per_sm * sms;
 }
-extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int grid, int block, cudaStream_t stream) {
-  hs_sweep_kernel<<<grid, block, 0, stream>>>(*ka, op);
+// mode: 0 general, 1 lane-per-device full, 2 lane-per-device order-free (see hs_sweep_kernel)
+extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int mode, int grid, int block, cudaStream_t stream) {
+  if (mode == 2) hs_sweep_kernel<2><<<grid, block, 0, stream>>>(*ka, op);
+  else if (mode == 1) hs_sweep_kernel<1><<<grid, block, 0, stream>>>(*ka, op);
+  else hs_sweep_kernel<0><<<grid, block, 0, stream>>>(*ka, op);
   return (int)cudaGetLastError();
 }
+extern "C" int hs_sweep_blocks_per_sm(int mode) { return mode == 0 ? 2 : (mode == 1 ? 4 : 6); }
 extern "C" int hs_launch_commit(const KernelArgs* ka, int op, unsigned long long win, cudaStream_t stream) {
   hs_commit_kernel<<<1, 32, 0, stream>>>(*ka, op, win);
   return (int)cudaGetLastError();

@@ -146,3 +146,40 @@ def test_branch_free_divide_matches_ieee():
     L.hs_debug_divcheck.restype = C.c_longlong
     L.hs_debug_divcheck.argtypes = [C.c_ulonglong, C.c_ulonglong]
     assert L.hs_debug_divcheck(1 << 28, 20260601) == 0
+
+
+def test_sweep_probe_matches_oracle_choice():
+    # the sweep-only kernel (HBM scan probe / sharded step) must pick the node the oracle's Filter picks
+    import ctypes as C
+    import k8s_vgpu_scheduler_b200.engine as eng
+    import oracle_abi as oa
+    cfg, nodes, ops = _gen().config3(n_nodes=200, n_pods=600)
+    o = oa.Oracle(cfg["node_policy"], cfg["gpu_policy"])
+    e = eng.Engine(cfg["node_policy"], cfg["gpu_policy"])
+    for n in nodes:
+        o.node_upsert(n)
+        e.node_upsert(n)
+    fill = ops[:400]
+    e.run_batch(eng.PackedOps(fill))
+    for kind, arg in fill:
+        o.filter(arg) if kind == "filter" else o.pod_delete(arg)
+    L = eng.lib()
+    L.hs_sweep_probe.argtypes = [C.c_void_p, C.POINTER(abi.hs_pod), C.c_uint32, C.POINTER(C.c_double),
+                                 C.POINTER(C.c_int32), C.POINTER(C.c_float)]
+    checked = 0
+    for kind, arg in ops[400:]:
+        if kind != "filter":
+            continue
+        p, keep = abi.build_pod(dict(arg, uid="probe-only"))
+        ms, idx, sc = C.c_double(), C.c_int32(), C.c_float()
+        rc = L.hs_sweep_probe(e.h, C.byref(p), 1, C.byref(ms), C.byref(idx), C.byref(sc))
+        r = o.filter(dict(arg, uid="probe-only"))
+        o.pod_delete("probe-only")       # the probe does not commit: undo the oracle's commit
+        assert rc == r["status"]
+        if rc == abi.HS_FIT:
+            assert idx.value == r["node_index"] and parity.f32bits(sc.value) == parity.f32bits(r["score"])
+        checked += 1
+        if checked >= 60:
+            break
+    o.close()
+    e.close()
