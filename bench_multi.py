@@ -1,0 +1,116 @@
+"""bench.py --gpus N (N > 1): the sharded path of SURVEY §8e on ONE node, one process per GPU (torchrun).
+
+Workload: C5 — a 100,000-node synthetic inventory (C2's device and request mix) partitioned in contiguous
+node blocks across the ranks.  Every rank sees the same pod stream; per decision each rank's sweep kernel
+produces its packed (score, global position) key, an NCCL all-reduce(MAX, uint64) over NVLink merges the
+keys in place, and the rank that owns the winning node commits.  The whole batch is enqueued on the engine's
+stream without host synchronisation; time = CUDA events, MAX over ranks.  scaling: "strong" (the inventory
+and the stream are fixed as N grows).
+"""
+import json
+import os
+import statistics
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_NODES = 100000
+BATCH_OPS = 1024
+FILL_FILTERS = 4096
+
+
+def partition(n_nodes, world):
+    """contiguous blocks, block not cyclic: 'highest index wins' == highest rank, then highest local index"""
+    per = (n_nodes + world - 1) // world
+    return [(r * per, min(n_nodes, (r + 1) * per)) for r in range(world)]
+
+
+def run(args, world, rank, local_rank):
+    import torch
+    import torch.distributed as dist
+    import k8s_vgpu_scheduler_b200.engine as eng
+    import k8s_vgpu_scheduler_b200.gen as gen
+    import bench as B
+
+    if world != args.gpus:
+        raise SystemExit("launch with torchrun --nproc-per-node %d" % args.gpus)
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    n_nodes = args.nodes if args.nodes != B.N_NODES else N_NODES
+    batch = min(args.batch, BATCH_OPS)
+    n_pods = FILL_FILTERS + (args.warmup + args.steps + 1) * batch
+    cfg, nodes, ops = gen.config5(n_nodes=n_nodes, n_pods=n_pods)
+    lo, hi = partition(n_nodes, world)[rank]
+
+    e = eng.Engine(cfg["node_policy"], cfg["gpu_policy"], cuda_device=local_rank, reserve_nodes=hi - lo)
+    for n in nodes[lo:hi]:
+        e.node_upsert(n)
+    uid = [eng.unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(uid, src=0)
+    e.shard_init(rank, world, uid[0], lo)
+
+    cnt, cut = 0, 0
+    for i, (k, _) in enumerate(ops):
+        if k == "filter":
+            cnt += 1
+            if cnt == FILL_FILTERS:
+                cut = i + 1
+                break
+    fill, rest = ops[:cut], ops[cut:]
+    batches = [rest[i * batch:(i + 1) * batch] for i in range(args.warmup + args.steps)]
+    packed = [eng.PackedOps(b) for b in batches]
+    e.run_batch(eng.PackedOps(fill))
+    for i in range(args.warmup):
+        e.run_batch(packed[i])
+
+    sampler = B.ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = e.launch_count()
+    dev_ms, e2e_s, decisions, fits, nofits, remote = [], [], 0, 0, 0, 0
+    dist.barrier()
+    torch.cuda.synchronize()
+    for i in range(args.warmup, args.warmup + args.steps):
+        t0 = time.perf_counter()
+        e.run_batch(packed[i])
+        nf, nn, _ = e.batch_summary(digest=False)
+        t1 = time.perf_counter()
+        e2e_s.append(t1 - t0)
+        dev_ms.append(e.last_device_ms())
+        decisions += sum(1 for k, _ in batches[i] if k == "filter")
+        fits += nf
+        nofits += nn
+    torch.cuda.synchronize()
+    dist.barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = e.launch_count() - launches0
+    # MAX over ranks of the device time and of the end-to-end time; fits are owned by exactly one rank each
+    t = torch.tensor([sum(dev_ms), sum(e2e_s)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    c = torch.tensor([fits, nofits], dtype=torch.int64, device="cuda")
+    dist.all_reduce(c, op=dist.ReduceOp.SUM)
+    total_dev_s, total_e2e_s = float(t[0]) / 1e3, float(t[1])
+    if rank == 0:
+        peak, peak_src = B.measured_peak()
+        bytes_alg = decisions * (n_nodes * 8 * 32)
+        out = {
+            "metric": B.METRIC, "value": round(decisions / total_dev_s, 1), "unit": B.UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * total_dev_s / args.steps, 4),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32+f32", "data": "synthetic",
+            "config": {"workload": "C5: %d-node inventory (C2 device/request mix) sharded in contiguous blocks over %d GPUs; "
+                                   "per decision sweep -> NCCL allreduce(MAX,uint64) -> owner commit" % (n_nodes, world),
+                       "ops_per_step": batch, "decisions_timed": decisions, "fits": int(c[0]),
+                       "no_fits": int(c[1]) // world, "l2": "each rank's shard (%.1f MB) is L2 resident" % ((hi - lo) * 256 / 1e6)},
+            "e2e": {"value": round(decisions / total_e2e_s, 1), "unit": B.UNIT,
+                    "h2d_bytes_per_step": batch * 160, "d2h_bytes_per_step": batch * 160},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": round(bytes_alg / total_dev_s / 1e9, 1), "peak": peak * world,
+                         "unit": "GB/s", "frac": round(bytes_alg / total_dev_s / 1e9 / (peak * world), 4), "traffic": None,
+                         "peak_source": peak_src + " x n_gpus", "kernel": "hs_sweep_kernel",
+                         "note": "latency-bound: 3 kernel launches + one 8-byte NCCL allreduce per decision"},
+        }
+        print(json.dumps(out))
+    e.close()
+    dist.destroy_process_group()

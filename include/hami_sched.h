@@ -39,6 +39,7 @@ enum {
   HS_FIT = 0,            /* a node was chosen and committed               */
   HS_NOFIT = 1,          /* no node fits: FailedNodes is filled, no commit (scheduler.go:1109-1114) */
   HS_PASSTHROUGH = 2,    /* pod requests no HAMi resource: every candidate passes (scheduler.go:1080-1087) */
+  HS_FIT_REMOTE = 3,     /* sharded mode: a node on ANOTHER rank's shard was chosen; node_index = global position */
   HS_ERR_INVALID = -1,   /* malformed argument / unsupported shape        */
   HS_ERR_CUDA = -2,      /* CUDA runtime failure; see hs_last_error       */
   HS_ERR_UNSUPPORTED = -3,/* feature outside the built scope (MIG, quota…) */
@@ -278,6 +279,15 @@ int32_t hs_rollback(hs_handle* h, const char* pod_uid);
 /* Usage cache dump for one node, rows in device-slot order (metrics / parity;
  * the reference's equivalent is InspectAllNodesUsage, scheduler.go:630-639). */
 int32_t hs_snapshot_node(hs_handle* h, const char* node, hs_device_usage_row* rows, uint32_t cap);
+
+/* ---- sharded mode: one process per GPU, contiguous node blocks, NCCL allreduce-max per decision ----
+ * (no counterpart in the reference, which runs one scheduler replica).  Rank 0 creates the
+ * 128-byte NCCL unique id and ships it to the others (e.g. torch.distributed broadcast); every rank then
+ * calls hs_shard_init with the global candidate position of its first node.  Afterwards every rank must
+ * call hs_run_batch with the SAME ops; a decision is committed by the rank that owns the winning node and
+ * reported as HS_FIT_REMOTE by the others.                                                             */
+int32_t hs_shard_unique_id(void* out128);
+int32_t hs_shard_init(hs_handle* h, int32_t rank, int32_t world, const void* unique_id128, int64_t pos_base);
 
 /* ---- measurement / diagnostic hooks (no counterpart in the reference) ----------------------- */
 /* The inventory scan in isolation: compile `pod`, run the sweep-only kernel `iters` times over the

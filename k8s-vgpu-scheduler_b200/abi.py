@@ -6,7 +6,7 @@ computes anything; the engine lives in csrc/ (CUDA) behind libhami_sched.so.
 """
 import ctypes as C
 
-HS_FIT, HS_NOFIT, HS_PASSTHROUGH = 0, 1, 2
+HS_FIT, HS_NOFIT, HS_PASSTHROUGH, HS_FIT_REMOTE = 0, 1, 2, 3
 HS_ERR_INVALID, HS_ERR_CUDA, HS_ERR_UNSUPPORTED, HS_ERR_WEIGHTS, HS_ERR_NOTFOUND = -1, -2, -3, -4, -5
 HS_OP_FILTER, HS_OP_DELETE = 0, 1
 

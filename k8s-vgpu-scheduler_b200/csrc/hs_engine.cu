@@ -6,6 +6,7 @@
 // hs_kernels.cu only see the SoA inventory and integer request descriptors.
 // There is no CPU fallback: without a CUDA device hs_create fails.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
 #include <array>
@@ -26,7 +27,8 @@ extern "C" int hs_launch_decide(const KernelArgs* ka, int grid, int block, cudaS
 extern "C" int hs_decide_max_blocks(int block, int device);
 extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int mode, int grid, int block, cudaStream_t stream);
 extern "C" int hs_sweep_blocks_per_sm(int mode);
-extern "C" int hs_launch_commit(const KernelArgs* ka, int op, unsigned long long win, cudaStream_t stream);
+extern "C" int hs_launch_shard_decide(const KernelArgs* ka, int op, cudaStream_t stream);
+extern "C" int hs_launch_shard_explain(const KernelArgs* ka, int op, int grid, cudaStream_t stream);
 
 namespace {
 
@@ -228,6 +230,11 @@ struct hs_handle {
   DBuf<int32_t> b_candpos;
   DBuf<unsigned long long> b_timing;   // HS_TIMING=1: phase clocks of block 0
   bool timing = false;
+  // sharded mode (one process per GPU): contiguous node block per rank, NCCL allreduce-max of the packed key per decision
+  int shard_rank = 0, shard_world = 1;
+  int64_t pos_base = 0;
+  void* nccl_comm = nullptr;
+  bool force_shard = false;  // HS_FORCE_SHARD=1: run the sharded pipeline (sweep / decide / explain kernels) with world == 1
   double host_s[4] = {0, 0, 0, 0};      // diagnostic: cumulative host seconds in compile / device+copies / absorb / summary
   uint32_t fail_cap = 32;
   std::vector<OpMeta> metas;            // per device op
@@ -645,7 +652,7 @@ int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_ca
   ka.commit_delta = h->b_delta.d; ka.sync = h->b_best.d;
   ka.fail = h->b_fail.d; ka.fail_cap = h->fail_cap;
   ka.counters = h->b_counters.d;
-  ka.pos_base = 0;
+  ka.pos_base = (int32_t)h->pos_base;
   ka.timing = h->timing ? h->b_timing.d : nullptr;
   return HS_OK;
 }
@@ -721,6 +728,103 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
   }
   if (alloc_base) CUDA_OK(h, cudaMemcpy(h->b_alloc.h, h->b_alloc.d, (size_t)std::min(alloc_base, alloc_cap) * sizeof(DevAlloc), cudaMemcpyDeviceToHost));
   CUDA_OK(h, cudaMemcpy(h->b_delta.h, h->b_delta.d, (size_t)n_ops * HS_D * sizeof(int4), cudaMemcpyDeviceToHost));
+  return HS_OK;
+}
+
+// ---- NCCL, bound at run time (whichever libnccl.so.2 the process already has: torch's or the system's) ----
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, struct NcclId, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+struct NcclId { char internal[128]; };
+NcclApi g_nccl;
+bool nccl_load(std::string& err) {
+  if (g_nccl.lib) return true;
+  void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!lib) { err = std::string("dlopen libnccl.so.2: ") + dlerror(); return false; }
+  g_nccl.GetUniqueId = (int (*)(void*))dlsym(lib, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (int (*)(void**, int, NcclId, int))dlsym(lib, "ncclCommInitRank");
+  g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(lib, "ncclAllReduce");
+  g_nccl.CommDestroy = (int (*)(void*))dlsym(lib, "ncclCommDestroy");
+  g_nccl.GetErrorString = (const char* (*)(int))dlsym(lib, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce) { err = "libnccl.so.2 lacks the expected symbols"; return false; }
+  g_nccl.lib = lib;
+  return true;
+}
+
+// Sharded run of the staged device ops: per FILTER op sweep → allreduce(max) → decide → explain, all enqueued
+// on the engine's stream with no host synchronisation in between; one sync at the end.
+int run_device_ops_sharded(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, size_t n_rel, uint32_t alloc_cap) {
+  int rc = flush_inventory(h);
+  if (rc != HS_OK) return rc;
+  const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
+  const int nn = std::max(n_nodes, HS_TILE);
+  // no resume in this mode: size the FailedNodes buffer for the batch (bounded at 64 MB)
+  const uint32_t shard_fail_cap = (uint32_t)std::min<size_t>((size_t)n_ops, std::max<size_t>(h->fail_cap, (64u << 20) / ((size_t)nn * sizeof(DevFail))));
+  if (!h->b_dec.ensure(n_ops) || !h->b_alloc.ensure(std::max<uint32_t>(alloc_cap, 1)) || !h->b_delta.ensure((size_t)n_ops * HS_D) ||
+      !h->b_best.ensure(n_ops) || !h->b_counters.ensure(8) || !h->b_fail.ensure((size_t)shard_fail_cap * nn)) {
+    h->err = "out of device memory for batch buffers";
+    return HS_ERR_CUDA;
+  }
+  CUDA_OK(h, cudaMemcpyAsync(h->b_pods.d, h->b_pods.h, (size_t)n_ops * sizeof(DevPod), cudaMemcpyHostToDevice, h->stream));
+  if (n_entries) CUDA_OK(h, cudaMemcpyAsync(h->b_entries.d, h->b_entries.h, n_entries * sizeof(DevEntry), cudaMemcpyHostToDevice, h->stream));
+  if (n_uuid) CUDA_OK(h, cudaMemcpyAsync(h->b_uuid.d, h->b_uuid.h, n_uuid * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+  if (n_rel) CUDA_OK(h, cudaMemcpyAsync(h->b_rel.d, h->b_rel.h, n_rel * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, cudaMemsetAsync(h->b_dec.d, 0xff, (size_t)n_ops * sizeof(DevDecision), h->stream));
+  CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, (size_t)n_ops * sizeof(OpSync), h->stream));
+  CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
+  KernelArgs ka;
+  build_kernel_args(h, ka, n_ops, alloc_cap);
+  ka.fail_cap = shard_fail_cap;
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+  const int block = 256;
+  CUDA_OK(h, cudaEventRecord(h->ev0, h->stream));
+  for (int op = 0; op < n_ops; op++) {
+    const DevPod& p = h->b_pods.h[op];
+    cudaError_t le = cudaSuccess;
+    if (p.op == OP_FILTER) {
+      const int mode = !p.fast ? 0 : (((p.flags & PF_NUMA_ASSERT) && p.e0.vendor == HV_NVIDIA) ? 1 : 2);
+      const int grid = std::max(1, std::min(sms * hs_sweep_blocks_per_sm(mode), (n_nodes * HS_D + block - 1) / block));
+      le = (cudaError_t)hs_launch_sweep(&ka, op, mode, grid, block, h->stream);
+      if (le == cudaSuccess && h->shard_world > 1) {
+        int nr = g_nccl.AllReduce(&h->b_best.d[op].best, &h->b_best.d[op].best, 1, 5 /*ncclUint64*/, 2 /*ncclMax*/, h->nccl_comm, h->stream);
+        if (nr != 0) { h->err = std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nr) : "?"); return HS_ERR_CUDA; }
+      }
+      if (le == cudaSuccess) le = (cudaError_t)hs_launch_shard_decide(&ka, op, h->stream);
+      if (le == cudaSuccess) le = (cudaError_t)hs_launch_shard_explain(&ka, op, std::max(1, std::min(sms * 2, (n_nodes * HS_D + 255) / 256)), h->stream);
+      h->launches += 3;
+    } else {
+      le = (cudaError_t)hs_launch_shard_decide(&ka, op, h->stream);
+      h->launches += 1;
+    }
+    if (le != cudaSuccess) { h->err = std::string("sharded launch: ") + cudaGetErrorString(le); return HS_ERR_CUDA; }
+  }
+  CUDA_OK(h, cudaEventRecord(h->ev1, h->stream));
+  CUDA_OK(h, cudaMemcpyAsync(h->b_counters.h, h->b_counters.d, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_OK(h, cudaMemcpyAsync(h->b_dec.h, h->b_dec.d, (size_t)n_ops * sizeof(DevDecision), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_OK(h, cudaMemcpyAsync(h->b_delta.h, h->b_delta.d, (size_t)n_ops * HS_D * sizeof(int4), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_OK(h, cudaStreamSynchronize(h->stream));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+  h->last_ms = ms;
+  const uint32_t nalloc = std::min(h->b_counters.h[0], alloc_cap);
+  if (nalloc) CUDA_OK(h, cudaMemcpy(h->b_alloc.h, h->b_alloc.d, (size_t)nalloc * sizeof(DevAlloc), cudaMemcpyDeviceToHost));
+  const uint32_t nfail = std::min(h->b_counters.h[1], shard_fail_cap);
+  h->fail_host.clear();
+  h->op_fail_slot.assign(n_ops, 0xffffffffu);
+  if (nfail) {
+    h->fail_host.resize((size_t)nfail * n_nodes);
+    CUDA_OK(h, cudaMemcpy(h->fail_host.data(), h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail), cudaMemcpyDeviceToHost));
+  }
+  for (int op = 0; op < n_ops; op++) {
+    const DevDecision& d = h->b_dec.h[op];
+    if (d.status == 1 && d.fail_slot < nfail) h->op_fail_slot[op] = d.fail_slot;
+  }
   return HS_OK;
 }
 
@@ -893,6 +997,10 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
       }
     }
     for (auto& kv : annos) h->r_annos.push_back(hs_kv{h->keep(kv.first), h->keep(kv.second)});
+  } else if (dec.status == 3) {
+    out->status = HS_FIT_REMOTE;      // sharded: the chosen node lives on another rank; node_index is its global position
+    out->node_index = dec.node;
+    out->score = dec.score;
   } else if (dec.status == 1) {
     out->status = HS_NOFIT;
     uint32_t slot = h->op_fail_slot[op];
@@ -933,7 +1041,17 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
     in_batch.erase(ib);
   } else {
     auto it = h->pods.find(uid);
-    if (it == h->pods.end()) return false;
+    if (it == h->pods.end()) {
+      if (h->shard_world <= 1 || user_op < 0) return false;
+      p.op = OP_NOP;                       // sharded: another rank may hold it; keep the op index aligned across ranks
+      OpMeta m;
+      m.kind = OP_NOP;
+      m.uid = uid;
+      m.user_op = user_op;
+      pods.push_back(p);
+      metas.push_back(m);
+      return true;
+    }
     p.rel_node = it->second.node;
     p.rel_off = (int32_t)rel.size();
     for (int d = 0; d < HS_D; d++) rel.push_back(it->second.delta[d]);
@@ -1021,7 +1139,8 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
   if (!uuid_pool.empty()) memcpy(h->b_uuid.h, uuid_pool.data(), uuid_pool.size() * sizeof(uint32_t));
   if (!rel.empty()) memcpy(h->b_rel.h, rel.data(), rel.size() * sizeof(int4));
   const double t1 = now_s();
-  int rc = run_device_ops(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap);
+  int rc = (h->shard_world > 1 || h->force_shard) ? run_device_ops_sharded(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap)
+                              : run_device_ops(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap);
   if (rc != HS_OK) return rc;
   const double t2 = now_s();
   absorb_results(h, n);
@@ -1074,6 +1193,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   const char* blk = getenv("HS_BLOCK");
   if (blk) { int b = atoi(blk); if (b >= 32 && b <= 512 && b % 32 == 0) h->block = b; }
   h->no_fast = getenv("HS_NO_FAST") != nullptr;
+  h->force_shard = getenv("HS_FORCE_SHARD") != nullptr;
   if (getenv("HS_TIMING") && h->b_timing.ensure(16)) { h->timing = true; cudaMemset(h->b_timing.d, 0, 16 * sizeof(unsigned long long)); }
   const char* fc = getenv("HS_FAIL_CAP");
   if (fc && atoi(fc) > 0) h->fail_cap = (uint32_t)atoi(fc);
@@ -1093,6 +1213,7 @@ void hs_destroy(hs_handle* h) {
   h->b_pods.release(); h->b_entries.release(); h->b_uuid.release(); h->b_rel.release(); h->b_dec.release();
   h->b_alloc.release(); h->b_delta.release(); h->b_best.release(); h->b_fail.release(); h->b_counters.release();
   h->b_candpos.release(); h->b_timing.release();
+  if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -1429,6 +1550,26 @@ int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* 
 int32_t hs_debug_host_seconds(hs_handle* h, double out[4]) {
   if (!h) return HS_ERR_INVALID;
   for (int i = 0; i < 4; i++) out[i] = h->host_s[i];
+  return HS_OK;
+}
+
+int32_t hs_shard_unique_id(void* out128) {
+  std::string err;
+  if (!out128 || !nccl_load(err)) { g_create_error = err; return HS_ERR_CUDA; }
+  return g_nccl.GetUniqueId(out128) == 0 ? HS_OK : HS_ERR_CUDA;
+}
+
+int32_t hs_shard_init(hs_handle* h, int32_t rank, int32_t world, const void* unique_id128, int64_t pos_base) {
+  if (!h || world < 1 || rank < 0 || rank >= world) return HS_ERR_INVALID;
+  cudaSetDevice(h->device);
+  h->shard_rank = rank; h->shard_world = world; h->pos_base = pos_base;
+  if (world == 1) return HS_OK;
+  if (!unique_id128) return HS_ERR_INVALID;
+  if (!nccl_load(h->err)) return HS_ERR_CUDA;
+  NcclId id;
+  memcpy(&id, unique_id128, sizeof id);
+  int nr = g_nccl.CommInitRank(&h->nccl_comm, world, id, rank);
+  if (nr != 0) { h->err = std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nr) : "?"); return HS_ERR_CUDA; }
   return HS_OK;
 }
 

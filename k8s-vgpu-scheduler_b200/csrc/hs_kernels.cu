@@ -513,34 +513,75 @@ hs_sweep_kernel(const KernelArgs ka, int op) {
   }
 }
 
-// Commit / explain for a winner chosen outside the kernel (sharded path: the key was merged
-// across ranks; only the rank whose shard holds the position commits).
+// ---- sharded path (one process per GPU, nodes partitioned in contiguous blocks) -----------------
+// Per op the host enqueues, with no host synchronisation in between:
+//   hs_sweep_kernel            → this rank's arg-best key in sync[op].best
+//   ncclAllReduce(MAX, uint64) → the global winner in place (the key embeds the GLOBAL position, so max
+//                                implements the canonical tie-break across ranks)
+//   hs_shard_decide_kernel     → the rank whose shard holds the position commits; the others record "remote"
+//   hs_shard_explain_kernel    → only does work when no rank fits: this shard's FailedNodes reasons
+// RELEASE ops need only the decide kernel.
 extern "C" __global__ void __launch_bounds__(32)
-hs_commit_kernel(const KernelArgs ka, int op, unsigned long long win) {
-  __shared__ DevPod s_pod;
-  __shared__ DevEntry s_ent[HS_MAX_E];
+hs_shard_decide_kernel(const KernelArgs ka, int op) {
+  __shared__ __align__(16) DevPod s_pod;
+  __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.pods + op);
     uint32_t* dst = reinterpret_cast<uint32_t*>(&s_pod);
     for (int i = threadIdx.x; i < (int)(sizeof(DevPod) / 4); i += blockDim.x) dst[i] = src[i];
   }
   __syncthreads();
-  {
-    const int ne = s_pod.n_entries;
+  const DevEntry* ent = &s_pod.e0;
+  if (s_pod.op == OP_FILTER && s_pod.n_entries > 1) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.entries + s_pod.entry_off);
     uint32_t* dst = reinterpret_cast<uint32_t*>(s_ent);
-    for (int i = threadIdx.x; i < ne * (int)(sizeof(DevEntry) / 4); i += blockDim.x) dst[i] = src[i];
+    for (int i = threadIdx.x; i < s_pod.n_entries * (int)(sizeof(DevEntry) / 4); i += blockDim.x) dst[i] = src[i];
+    __syncthreads();
+    ent = s_ent;
   }
-  __syncthreads();
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (threadIdx.x != 0) return;
+  DevDecision dec;
+  dec.status = 2; dec.node = -1; dec.score = 0; dec.alloc_off = 0; dec.n_alloc = 0; dec.fail_slot = 0xffffffffu;
+  dec.pad[0] = dec.pad[1] = 0;
+  if (s_pod.op == OP_RELEASE) {
+    int node = s_pod.rel_node;
+    const int4* rows;
+    if (node >= 0) rows = ka.rel_pool + s_pod.rel_off;
+    else {
+      node = ka.decisions[s_pod.rel_ref].status == 0 ? ka.decisions[s_pod.rel_ref].node : -1;   // only the owner rank committed it
+      rows = ka.commit_delta + (size_t)s_pod.rel_ref * HS_D;
+    }
+    if (node >= 0 && node < ka.n_nodes) {
+      int4 delta[HS_D];
+      for (int d = 0; d < HS_D; d++) delta[d] = rows[d];
+      store_usage(ka, node, delta, -1);
+    }
+    ka.decisions[op] = dec;
+    return;
+  }
+  if (s_pod.op != OP_FILTER) { ka.decisions[op] = dec; return; }
+  const unsigned long long win = ka.sync[op].best;   // merged across ranks
+  if (!KEY_VALID(win)) {
+    dec.status = 1;
+    dec.fail_slot = atomicAdd(ka.counters + 1, 1u);  // this shard's slot in the fail buffer (may exceed fail_cap: not recorded)
+    ka.decisions[op] = dec;
+    return;
+  }
   const int pos = KEY_POS(win) - ka.pos_base;
   int node = -1;
-  if (!ka.cand_pos) node = pos;
-  else for (int n = 0; n < ka.n_nodes; n++) if (ka.cand_pos[n] == pos) { node = n; break; }
-  DevDecision dec;
-  dec.status = -1; dec.node = node; dec.score = 0; dec.alloc_off = 0; dec.n_alloc = 0; dec.fail_slot = 0xffffffffu;
-  dec.pad[0] = dec.pad[1] = 0;
-  if (node >= 0 && node < ka.n_nodes) {
+  if (pos >= 0 && pos < ka.n_nodes) {
+    if (!ka.cand_pos) node = pos;
+    else for (int n = 0; n < ka.n_nodes; n++) if (ka.cand_pos[n] == pos) { node = n; break; }
+  }
+  dec.status = 3;                                    // fits on another rank's shard
+  dec.node = KEY_POS(win);                           // global position
+  {
+    uint32_t u = (uint32_t)(win >> 32);
+    if (s_pod.flags & PF_NODE_SPREAD) u = ~u;
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+    dec.score = __uint_as_float(u);
+  }
+  if (node >= 0 && (ka.node_flags[node] & NF_ALIVE)) {
     const uint32_t nf = ka.node_flags[node];
     NodeWork w;
     load_node(ka, node, nf, w);
@@ -548,17 +589,74 @@ hs_commit_kernel(const KernelArgs ka, int op, unsigned long long win) {
     EvalOut out;
     out.allocs = la; out.n_alloc = 0;
     float sc;
-    if (dev_score_node<EV_RECORD>(w, s_pod, s_ent, (uint32_t)node, nf, ka, out, &sc)) {
+    if (dev_score_node<EV_RECORD>(w, s_pod, ent, (uint32_t)node, nf, ka, out, &sc)) {
       const uint32_t off = atomicAdd(ka.counters + 0, out.n_alloc);
       for (uint32_t i = 0; i < out.n_alloc && off + i < ka.alloc_cap; i++) ka.allocs[off + i] = la[i];
       int4 delta[HS_D];
-      collapse_rows(s_ent, la, out.n_alloc, delta);
+      collapse_rows(ent, la, out.n_alloc, delta);
       store_usage(ka, node, delta, +1);
       for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)op * HS_D + d] = delta[d];
-      dec.status = 0; dec.score = sc; dec.alloc_off = off; dec.n_alloc = out.n_alloc;
+      dec.status = 0; dec.node = node; dec.score = sc; dec.alloc_off = off; dec.n_alloc = out.n_alloc;
+    } else {
+      dec.status = -1;                               // the sweep and the commit disagree: must not happen
     }
   }
   ka.decisions[op] = dec;
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+hs_shard_explain_kernel(const KernelArgs ka, int op) {
+  if (ka.decisions[op].status != 1) return;          // written by hs_shard_decide_kernel earlier on this stream
+  const uint32_t slot = ka.decisions[op].fail_slot;
+  if (slot >= ka.fail_cap) return;
+  __shared__ __align__(16) DevPod s_pod;
+  __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.pods + op);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&s_pod);
+    for (int i = threadIdx.x; i < (int)(sizeof(DevPod) / 4); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  const DevEntry* ent = &s_pod.e0;
+  if (s_pod.n_entries > 1) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.entries + s_pod.entry_off);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(s_ent);
+    for (int i = threadIdx.x; i < s_pod.n_entries * (int)(sizeof(DevEntry) / 4); i += blockDim.x) dst[i] = src[i];
+    __syncthreads();
+    ent = s_ent;
+  }
+  DevFail* fb = ka.fail + (size_t)slot * ka.n_nodes;
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int glane = threadIdx.x & 7;
+  const int gg = gtid >> 3, ngroups = (gridDim.x * blockDim.x) >> 3;
+  DevFail nc;
+  nc.kind_cards = FK_NOT_CANDIDATE; nc.c0 = nc.c1 = nc.pad = 0;
+  if (s_pod.fast) {
+    DevRegs n;
+    for (int node = gg; node < ka.n_nodes; node += ngroups) {   // warp-uniform trip count (n_nodes % 32 == 0)
+      const uint32_t nf = ka.node_flags[node];
+      const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
+      load_dev(ka, node, glane, n);
+      const DevFail f = fast_explain(n, glane, (uint32_t)node, nf, s_pod, s_pod.e0, ka);
+      if (glane == 0) fb[node] = pos >= 0 ? f : nc;
+    }
+  } else if (glane == 0) {
+    NodeWork w;
+    EvalOut out;
+    for (int node = gg; node < ka.n_nodes; node += ngroups) {
+      const uint32_t nf = ka.node_flags[node];
+      DevFail f = nc;
+      const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
+      if (pos >= 0) {
+        load_node(ka, node, nf, w);
+        out.fkind = FK_NONE; out.fcards = 0;
+        float sc;
+        dev_score_node<EV_EXPLAIN>(w, s_pod, ent, (uint32_t)node, nf, ka, out, &sc);
+        pack_fail(out, f);
+      }
+      fb[node] = f;
+    }
+  }
 }
 
 // Self-check of the branch-free divide (hs_fast.cuh) against the IEEE divide, over the operand space the
@@ -613,7 +711,11 @@ extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int mode, int grid,
   return (int)cudaGetLastError();
 }
 extern "C" int hs_sweep_blocks_per_sm(int mode) { return mode == 0 ? 2 : (mode == 1 ? 4 : 6); }
-extern "C" int hs_launch_commit(const KernelArgs* ka, int op, unsigned long long win, cudaStream_t stream) {
-  hs_commit_kernel<<<1, 32, 0, stream>>>(*ka, op, win);
+extern "C" int hs_launch_shard_decide(const KernelArgs* ka, int op, cudaStream_t stream) {
+  hs_shard_decide_kernel<<<1, 32, 0, stream>>>(*ka, op);
+  return (int)cudaGetLastError();
+}
+extern "C" int hs_launch_shard_explain(const KernelArgs* ka, int op, int grid, cudaStream_t stream) {
+  hs_shard_explain_kernel<<<grid, 256, 0, stream>>>(*ka, op);
   return (int)cudaGetLastError();
 }

@@ -17,7 +17,8 @@ _lib = None
 EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_batch_get", "hs_rollback",
-    "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary",
+    "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
+    "hs_shard_unique_id", "hs_shard_init", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
 ]
 
 
@@ -44,6 +45,8 @@ def lib():
     L.hs_run_batch.argtypes = [C.c_void_p, P(abi.hs_op), C.c_uint32]
     L.hs_batch_get.argtypes = [C.c_void_p, C.c_uint32, P(abi.hs_filter_result)]
     L.hs_batch_summary.argtypes = [C.c_void_p, P(C.c_uint32), P(C.c_uint32), P(C.c_uint64)]
+    L.hs_shard_unique_id.argtypes = [C.c_void_p]
+    L.hs_shard_init.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64]
     L.hs_rollback.argtypes = [C.c_void_p, C.c_char_p]
     L.hs_snapshot_node.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_device_usage_row), C.c_uint32]
     L.hs_last_device_ms.restype = C.c_double
@@ -52,6 +55,15 @@ def lib():
     L.hs_launch_count.argtypes = [C.c_void_p]
     _lib = L
     return L
+
+
+def unique_id():
+    """128-byte NCCL unique id (rank 0 creates it, the others receive it)."""
+    buf = C.create_string_buffer(128)
+    rc = lib().hs_shard_unique_id(buf)
+    if rc != 0:
+        raise RuntimeError("hs_shard_unique_id failed: %s" % lib().hs_last_error(None).decode())
+    return buf.raw
 
 
 class PackedOps:
@@ -150,6 +162,11 @@ class Engine:
         nf, nn, dg = C.c_uint32(), C.c_uint32(), C.c_uint64()
         self._check(self.L.hs_batch_summary(self.h, C.byref(nf), C.byref(nn), C.byref(dg) if digest else None))
         return nf.value, nn.value, dg.value
+
+    def shard_init(self, rank, world, unique_id, pos_base):
+        """unique_id: 128 bytes from unique_id() on rank 0 (None when world == 1)."""
+        buf = C.create_string_buffer(bytes(unique_id), 128) if unique_id is not None else None
+        return self._check(self.L.hs_shard_init(self.h, rank, world, buf, pos_base))
 
     def snapshot(self, node, cap=16):
         rows = (abi.hs_device_usage_row * cap)()

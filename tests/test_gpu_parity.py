@@ -183,3 +183,13 @@ def test_sweep_probe_matches_oracle_choice():
             break
     o.close()
     e.close()
+
+
+@pytest.mark.parametrize("name,kw", [("c1", dict(n_pods=300, departures=0.3)), ("c3", dict(n_nodes=150, n_pods=800)),
+                                     ("c4", dict(n_nodes=200, n_pods=1200)), ("mixed", dict())])
+def test_sharded_pipeline_single_rank(name, kw, monkeypatch):
+    # the multi-GPU pipeline (sweep kernel → [allreduce] → decide kernel → explain kernel) with one rank:
+    # same decisions as the oracle, bit for bit
+    monkeypatch.setenv("HS_FORCE_SHARD", "1")
+    cfg, nodes, ops = _gen().CONFIGS[name](**kw)
+    _check(cfg, nodes, ops)
