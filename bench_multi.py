@@ -24,7 +24,7 @@ FILL_FILTERS = 4096
 def partition(n_nodes, world):
     """contiguous blocks, block not cyclic: 'highest index wins' == highest rank, then highest local index"""
     per = (n_nodes + world - 1) // world
-    return [(r * per, min(n_nodes, (r + 1) * per)) for r in range(world)]
+    return [(min(n_nodes, r * per), min(n_nodes, (r + 1) * per)) for r in range(world)]
 
 
 def run(args, world, rank, local_rank):
