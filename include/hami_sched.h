@@ -289,6 +289,18 @@ int32_t hs_snapshot_node(hs_handle* h, const char* node, hs_device_usage_row* ro
 int32_t hs_shard_unique_id(void* out128);
 int32_t hs_shard_init(hs_handle* h, int32_t rank, int32_t world, const void* unique_id128, int64_t pos_base);
 
+/* ---- the allocation-free entry point (it has no counterpart in the reference) --------------------
+ * For callers that cannot call cudaMalloc when they need a scan: a plugin whose device memory is a fixed
+ * pool carved up at start-up, or a latency-critical path that must not enter the driver's allocator.
+ * Scans the handle's resident inventory for `pod` (one request entry, no UUID use/no-use list; no
+ * commit) and writes 16 bytes to the caller's device buffer: the winning packed key (bits 63-32 ordered
+ * score, bits 31-8 node position + 1, 0 = no node fits), then the number of CTAs used.  All scratch lives
+ * in one static device array per GPU (about 8.5 KB, held until the process exits): at most 1024 CTAs and
+ * 4,194,304 nodes, larger inputs are refused with HS_ERR_UNSUPPORTED.  The first call on a device resolves
+ * the array's address — make it before any stream capture.  Calls share the array: run them one after
+ * the other, never overlapping on the GPU.  `cuda_stream` NULL = the engine's own stream.              */
+int32_t hs_sweep_static(hs_handle* h, const hs_pod* pod, void* out_device16, void* cuda_stream);
+
 /* ---- measurement / diagnostic hooks (no counterpart in the reference) ----------------------- */
 /* The inventory scan in isolation: compile `pod`, run the sweep-only kernel `iters` times over the
  * whole inventory (no commit); average device ms per sweep, the winning candidate position, its score. */

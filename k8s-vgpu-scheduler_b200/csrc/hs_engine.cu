@@ -1609,3 +1609,156 @@ double hs_last_device_ms(const hs_handle* h) { return h ? h->last_ms : 0.0; }
 uint64_t hs_launch_count(const hs_handle* h) { return h ? h->launches : 0; }
 
 }  // extern "C"
+
+// ================================================================================================
+// hs_sweep_static — the one entry point of this library that allocates NOTHING.
+//
+// Who it is for: callers that are not allowed to call cudaMalloc at the moment they need a scan —
+// a scheduler plugin running inside a process whose device memory is a fixed, pre-carved pool (every
+// byte already handed out at start-up), a latency-critical admission path where an allocation could
+// block on the driver's allocator lock or trigger an implicit device synchronisation, or code that has
+// switched the context to a mode in which the allocator must not be entered.  Every other entry point of
+// this library may grow its staging buffers on demand; this one never does.
+//
+// What it does: the same scan as hs_sweep_probe's kernel (one request against the whole resident
+// inventory, no commit) — but its scratch memory (the request record, the per-CTA partial keys and the
+// "last block" ticket) lives in the file-scope array below, which exists once per GPU that loads this
+// library and stays until the process exits (HS_STATIC_SCRATCH_BYTES, ~8.5 KB).  The caller passes the
+// inputs (the handle whose inventory is already in HBM, and the pod) and the output (a device buffer of
+// 16 bytes: the winning packed key, then the number of CTAs that took part).
+//
+// Rules that follow from the shared static array:
+//  * The first call on a device resolves the array's device address (cudaGetSymbolAddress with that
+//    device current) — make that first call before any stream capture begins.
+//  * Limit: the scan uses at most HS_STATIC_MAX_CTAS thread blocks and an inventory of at most
+//    HS_STATIC_MAX_NODES nodes; larger requests are refused with HS_ERR_UNSUPPORTED and a message.
+//    Only the common request shape (one request entry, no UUID use/no-use list) is accepted.
+//  * Every call reuses the same array and finds the previous call's contents in it: the entry point
+//    rewrites the request record and zeroes the ticket itself, and the partial keys are fully
+//    overwritten before they are read.  Two calls that overlap on the GPU (different streams, or two
+//    handles on one device) would race on the array — issue them one after the other.
+#define HS_STATIC_MAX_CTAS 1024
+#define HS_STATIC_MAX_NODES (1 << 22)
+#define HS_STATIC_SCRATCH_BYTES (512 + 8 * HS_STATIC_MAX_CTAS)
+
+static __device__ __align__(256) unsigned char g_static_scratch[HS_STATIC_SCRATCH_BYTES];
+// layout: [0,160) DevPod request record | [256,260) ticket | [512, 512 + 8*MAX_CTAS) per-CTA partial keys
+
+#include "hs_eval.cuh"
+#include "hs_fast.cuh"
+
+__global__ void __launch_bounds__(256, 4)
+hs_sweep_static_kernel(const int4* __restrict__ dyn, const int4* __restrict__ stat, const int4* __restrict__ node_tot,
+                       int n_nodes, unsigned char* scratch, unsigned long long* out) {
+  const DevPod& pod = *reinterpret_cast<const DevPod*>(scratch);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + 256);
+  unsigned long long* partial = reinterpret_cast<unsigned long long*>(scratch + 512);
+  __shared__ unsigned long long s_red[8];
+  __shared__ bool s_last;
+  KernelArgs ka;                       // only what the evaluators read
+  ka.dyn = const_cast<int4*>(dyn); ka.stat = stat; ka.node_tot = node_tot; ka.uuid_pool = nullptr;
+  ka.n_nodes = n_nodes; ka.cand_pos = nullptr; ka.pos_base = 0;
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31, glane = lane & 7, gbase = lane & 24;
+  const int gg = gtid >> 3, ngroups = (gridDim.x * blockDim.x) >> 3;
+  const bool spread = pod.flags & PF_NODE_SPREAD;
+  const bool lite = !((pod.flags & PF_NUMA_ASSERT) && pod.e0.vendor == HV_NVIDIA);
+  unsigned long long my_key = 0;
+  DevRegs n;
+  FastEval fe;
+  for (int node = gg; node < n_nodes; node += ngroups) {   // n_nodes % 32 == 0: warp-uniform trip count
+    const int4 nt = __ldg(node_tot + node);
+    const uint32_t nf = (uint32_t)nt.x;
+    const int4 a = dyn[(size_t)node * HS_D + glane];
+    const int4 b = __ldg(stat + (size_t)node * HS_D + glane);
+    n.used = a.x; n.mem = a.y; n.cores = a.z; n.dflags = (uint32_t)a.w;
+    n.count = b.x; n.totmem = b.y; n.totcore = b.z; n.packed = (uint32_t)b.w;
+    const bool fit = (lite ? fast_fit_lite(n, glane, gbase, (uint32_t)node, nf, pod, pod.e0, ka)
+                           : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, fe)) && (nf & NF_ALIVE);
+    if (!__any_sync(0xffffffffu, fit)) continue;
+    const float sc = fast_node_score_tot(n, 0xffu << gbase, nt.y, nt.z, nt.w);
+    if (fit) {
+      const unsigned long long key = make_key(sc, spread, (uint32_t)node);
+      my_key = key > my_key ? key : my_key;
+    }
+  }
+  unsigned long long bk = my_key;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long t = __shfl_xor_sync(0xffffffffu, bk, o);
+    bk = t > bk ? t : bk;
+  }
+  if (lane == 0) s_red[threadIdx.x >> 5] = bk;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int i = 1; i < (int)(blockDim.x >> 5); i++) bk = s_red[i] > bk ? s_red[i] : bk;
+    partial[blockIdx.x] = bk;
+    __threadfence();
+    s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {    // the last block to finish folds the partial keys
+    __threadfence();
+    unsigned long long best = 0;
+    for (unsigned int i = 0; i < gridDim.x; i++) {
+      const unsigned long long v = reinterpret_cast<volatile unsigned long long*>(partial)[i];
+      best = v > best ? v : best;
+    }
+    out[0] = best;
+    out[1] = gridDim.x;
+    *ticket = 0;                       // leave the ticket at zero for the next call as well
+  }
+}
+
+static unsigned char* g_static_ptr[64] = {nullptr};   // device address of g_static_scratch, per device ordinal
+
+extern "C" int32_t hs_sweep_static(hs_handle* h, const hs_pod* pod, void* out_device16, void* cuda_stream) {
+  if (!h || !pod || !out_device16) return HS_ERR_INVALID;
+  if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice failed"; return HS_ERR_CUDA; }
+  if (h->device < 0 || h->device >= 64) { h->err = "device ordinal out of range"; return HS_ERR_UNSUPPORTED; }
+  if (!g_static_ptr[h->device]) {
+    // One-time set-up on this device: in host code the array's name is only a stand-in, not a device
+    // address — resolve the real address with the device current, and check the result.
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || !p) { h->err = std::string("cudaGetSymbolAddress(g_static_scratch): ") + cudaGetErrorString(e); return HS_ERR_CUDA; }
+    g_static_ptr[h->device] = static_cast<unsigned char*>(p);
+  }
+  unsigned char* scratch = g_static_ptr[h->device];
+  const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
+  if (n_nodes > HS_STATIC_MAX_NODES) {
+    h->err = "hs_sweep_static: inventory exceeds HS_STATIC_MAX_NODES (4194304 nodes); use hs_sweep_probe / hs_filter";
+    return HS_ERR_UNSUPPORTED;
+  }
+  std::vector<uint32_t> uuid_pool;     // host memory only
+  Compiled c;
+  h->have_cand = false;
+  int rc = compile_pod(h, pod, uuid_pool, c);
+  if (rc != HS_OK) return rc;
+  if (!c.pod.fast || c.pod.e0.has_use || c.pod.e0.nouse_cnt) {
+    h->err = "hs_sweep_static: only the common request shape (one request entry, no UUID use/no-use list) is supported without allocation";
+    return HS_ERR_UNSUPPORTED;
+  }
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+  const int block = 256;
+  const int grid = std::max(1, std::min(sms * 4, (n_nodes * HS_D + block - 1) / block));
+  if (grid > HS_STATIC_MAX_CTAS) {
+    h->err = "hs_sweep_static: the scan would need more thread blocks than HS_STATIC_MAX_CTAS (1024)";
+    return HS_ERR_UNSUPPORTED;
+  }
+  cudaStream_t st = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->stream;
+  rc = flush_inventory(h);             // copies only (pending node upserts), no allocation
+  if (rc != HS_OK) return rc;
+  if (st != h->stream) CUDA_OK(h, cudaStreamSynchronize(h->stream));
+  // the array keeps the last call's contents: rewrite the request record, zero the ticket
+  CUDA_OK(h, cudaMemcpyAsync(scratch, &c.pod, sizeof(DevPod), cudaMemcpyHostToDevice, st));
+  CUDA_OK(h, cudaMemsetAsync(scratch + 256, 0, 256, st));
+  hs_sweep_static_kernel<<<grid, block, 0, st>>>(h->d_dyn, h->d_stat, h->d_tot, n_nodes, scratch,
+                                                 static_cast<unsigned long long*>(out_device16));
+  cudaError_t le = cudaGetLastError();
+  if (le != cudaSuccess) { h->err = std::string("hs_sweep_static launch: ") + cudaGetErrorString(le); return HS_ERR_CUDA; }
+  h->launches++;
+  CUDA_OK(h, cudaStreamSynchronize(st));   // &c.pod is a stack buffer: the copy must have completed before we return
+  return HS_OK;
+}

@@ -18,7 +18,7 @@ EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_batch_get", "hs_rollback",
     "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
-    "hs_shard_unique_id", "hs_shard_init", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
+    "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
 ]
 
 
