@@ -585,11 +585,35 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
   return HS_OK;
 }
 
+// NodeScore.ComputeDefaultScore (policy/node_policy.go:106-130) on the host mirror, float32 like the device
+int host_node_score_bits(hs_handle* h, int node) {
+  int32_t used = 0, usedCore = 0, usedMem = 0, total = 0, totalCore = 0, totalMem = 0;
+  for (int d = 0; d < HS_D; d++) {
+    const int4& dy = h->h_dyn[inv_idx(node, d)];
+    const int4& st = h->h_stat[inv_idx(node, d)];
+    used += dy.x; usedMem += dy.y; usedCore += dy.z;
+    total += st.x; totalMem += st.y; totalCore += st.z;
+  }
+  float sc = 0.0f;
+  if (!(total == 0 || totalCore == 0 || totalMem == 0)) {
+    volatile float a = (float)used / (float)total;
+    volatile float b = (float)usedCore / (float)totalCore;
+    volatile float c = (float)usedMem / (float)totalMem;
+    volatile float s1 = a + b;
+    volatile float s2 = s1 + c;
+    sc = 10.0f * s2;
+  }
+  int bits;
+  memcpy(&bits, &sc, 4);
+  return bits;
+}
+
 void apply_host_delta(hs_handle* h, int node, const int4* delta, int sign) {
   for (int d = 0; d < HS_D; d++) {
     int4& v = h->h_dyn[inv_idx(node, d)];
     v.x += sign * delta[d].x; v.y += sign * delta[d].y; v.z += sign * delta[d].z;
   }
+  h->h_tot[node].y = host_node_score_bits(h, node);
 }
 
 std::string encode_pod_single(const std::vector<std::vector<const hs_alloc_entry*>>& pd) {
@@ -1320,9 +1344,7 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
   if (vnpu) nf |= NF_VNPU_CORE;
   h->h_flags[slot] = nf;
   {
-    int4 t = make_int4((int)nf, 0, 0, 0);
-    for (int d = 0; d < n; d++) { t.y += ns.devs[d].count; t.z += ns.devs[d].devcore; t.w += ns.devs[d].devmem; }
-    h->h_tot[slot] = t;
+    h->h_tot[slot] = make_int4((int)nf, host_node_score_bits(h, slot), 0, 0);
   }
   mark_dirty(h, slot);
   return HS_OK;
@@ -1648,7 +1670,7 @@ static __device__ __align__(256) unsigned char g_static_scratch[HS_STATIC_SCRATC
 #include "hs_fast.cuh"
 
 __global__ void __launch_bounds__(256, 4)
-hs_sweep_static_kernel(const int4* __restrict__ dyn, const int4* __restrict__ stat, const int4* __restrict__ node_tot,
+hs_sweep_static_kernel(const int4* __restrict__ dyn, const int4* __restrict__ stat, int4* node_tot,
                        int n_nodes, unsigned char* scratch, unsigned long long* out) {
   const DevPod& pod = *reinterpret_cast<const DevPod*>(scratch);
   unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + 256);
@@ -1675,8 +1697,7 @@ hs_sweep_static_kernel(const int4* __restrict__ dyn, const int4* __restrict__ st
     n.count = b.x; n.totmem = b.y; n.totcore = b.z; n.packed = (uint32_t)b.w;
     const bool fit = (lite ? fast_fit_lite(n, glane, gbase, (uint32_t)node, nf, pod, pod.e0, ka)
                            : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, fe)) && (nf & NF_ALIVE);
-    if (!__any_sync(0xffffffffu, fit)) continue;
-    const float sc = fast_node_score_tot(n, 0xffu << gbase, nt.y, nt.z, nt.w);
+    const float sc = __int_as_float(nt.y);   // ComputeDefaultScore, maintained by the commits
     if (fit) {
       const unsigned long long key = make_key(sc, spread, (uint32_t)node);
       my_key = key > my_key ? key : my_key;

@@ -91,6 +91,15 @@ __device__ __forceinline__ void store_usage(const KernelArgs& ka, int node, cons
   }
 }
 
+// Recompute ComputeDefaultScore of one node from HBM and publish it in node_tot (one thread; used where the
+// node is not register-resident).  The streamed sweeps read the score from there instead of re-deriving it.
+__device__ void refresh_node_score(const KernelArgs& ka, int node) {
+  NodeWork w;
+  load_node(ka, node, ka.node_flags[node], w);
+  w.ndev = HS_D;   // absent slots hold zeros
+  ka.node_tot[node].y = __float_as_int(node_default_score(w));
+}
+
 __device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -205,6 +214,7 @@ hs_decide_kernel(const KernelArgs ka) {
     if (resident && __any_sync(FULL, dirty || reload)) {   // warp-uniform: refresh what a commit/release changed
       if (reload && gg < ka.n_nodes) load_dev(ka, gg, glane, D);
       my_pre = fast_node_score(D);
+      if ((dirty || reload) && glane == 0 && gg < ka.n_nodes) ka.node_tot[gg].y = __float_as_int(my_pre);
       dirty = false; reload = false;
     }
     TICK(0);
@@ -232,6 +242,7 @@ hs_decide_kernel(const KernelArgs ka) {
           if (resident) { D.used -= delta.x; D.mem -= delta.y; D.cores -= delta.z; }
         }
         dirty = true;
+        if (!resident) { __syncwarp(gmask); if (glane == 0) refresh_node_score(ka, node); }
       }
       if (gtid == 0) { ka.decisions[r].status = 2; ka.decisions[r].n_alloc = 0; }
       TICK(1);
@@ -364,6 +375,7 @@ hs_decide_kernel(const KernelArgs ka) {
             ka.decisions[r] = dec;
           }
           dirty = true;
+          if (!resident) { __syncwarp(gmask); if (glane == 0) refresh_node_score(ka, my_node); }
         }
       } else if (mine) {
         if (glane == 0) {
@@ -372,6 +384,7 @@ hs_decide_kernel(const KernelArgs ka) {
           const uint32_t off = atomicAdd(ka.counters + 0, my_nalloc);
           for (uint32_t i = 0; i < my_nalloc && off + i < ka.alloc_cap; i++) ka.allocs[off + i] = la[i];
           store_usage(ka, my_node, delta, +1);
+          refresh_node_score(ka, my_node);
           for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)r * HS_D + d] = delta[d];
           DevDecision dec;
           dec.status = 0; dec.node = my_node; dec.score = my_score; dec.alloc_off = off; dec.n_alloc = my_nalloc;
@@ -431,6 +444,11 @@ hs_decide_kernel(const KernelArgs ka) {
     TICK(6);
   }
   prefetch_wait();
+  if (resident && __any_sync(FULL, dirty || reload)) {   // publish the score of nodes changed by the last ops
+    if (reload && gg < ka.n_nodes) load_dev(ka, gg, glane, D);
+    my_pre = fast_node_score(D);
+    if ((dirty || reload) && glane == 0 && gg < ka.n_nodes) ka.node_tot[gg].y = __float_as_int(my_pre);
+  }
   if (gtid == 0) { ka.counters[2] = (uint32_t)r; ka.counters[1] = fail_count; }
 }
 
@@ -442,7 +460,7 @@ hs_decide_kernel(const KernelArgs ka) {
 // MODE 0: general evaluator (one thread per node); 1: lane-per-device with sort+scan (numa-bind); 2: lane-per-device,
 // order-free verdict.  Separate instantiations keep the streaming kernels' register footprint small.
 template <int MODE>
-__global__ void __launch_bounds__(256, (MODE == 0 ? 2 : (MODE == 1 ? 4 : 6)))
+__global__ void __launch_bounds__(256, (MODE == 0 ? 2 : (MODE == 1 ? 4 : 5)))
 hs_sweep_kernel(const KernelArgs ka, int op) {
   __shared__ __align__(16) DevPod s_pod;
   __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
@@ -473,20 +491,36 @@ hs_sweep_kernel(const KernelArgs ka, int op) {
     constexpr bool lite = MODE == 2;
     DevRegs n;
     FastEval fe;
-    const uint32_t gmask = 0xffu << gbase;
-    for (int node = gg; node < ka.n_nodes; node += ngroups) {   // n_nodes % 32 == 0: warp-uniform trip count
-      const int4 nt = __ldg(ka.node_tot + node);                 // {flags, sum count, sum core, sum mem}: one broadcast load
+    // software pipeline: the next node's three loads are in flight while this node is evaluated
+    int node = gg;
+    int4 nt = make_int4(0, 0, 0, 0), a = nt, b = nt;
+    if (node < ka.n_nodes) {
+      nt = __ldg(ka.node_tot + node);
+      a = ka.dyn[(size_t)node * HS_D + glane];
+      b = __ldg(ka.stat + (size_t)node * HS_D + glane);
+    }
+    while (node < ka.n_nodes) {   // n_nodes % 32 == 0: warp-uniform trip count
+      const int next = node + ngroups;
+      int4 nt2 = make_int4(0, 0, 0, 0), a2 = nt2, b2 = nt2;
+      if (next < ka.n_nodes) {
+        nt2 = __ldg(ka.node_tot + next);
+        a2 = ka.dyn[(size_t)next * HS_D + glane];
+        b2 = __ldg(ka.stat + (size_t)next * HS_D + glane);
+      }
       const uint32_t nf = (uint32_t)nt.x;
       const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
-      load_dev(ka, node, glane, n);
+      n.used = a.x; n.mem = a.y; n.cores = a.z; n.dflags = (uint32_t)a.w;
+      n.count = b.x; n.totmem = b.y; n.totcore = b.z; n.packed = (uint32_t)b.w;
       const bool fit = (lite ? fast_fit_lite(n, glane, gbase, (uint32_t)node, nf, pod, pod.e0, ka)
                              : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, fe)) && pos >= 0;
-      if (!__any_sync(FULL, fit)) continue;
-      const float sc = fast_node_score_tot(n, gmask, nt.y, nt.z, nt.w);
-      if (fit) {
-        const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
-        my_key = key > my_key ? key : my_key;
+      {
+        const float sc = __int_as_float(nt.y);   // ComputeDefaultScore, maintained by the commits
+        if (fit) {
+          const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
+          my_key = key > my_key ? key : my_key;
+        }
       }
+      node = next; nt = nt2; a = a2; b = b2;
     }
   } else if (MODE == 0 && glane == 0) {
     NodeWork w;
@@ -555,6 +589,7 @@ hs_shard_decide_kernel(const KernelArgs ka, int op) {
       int4 delta[HS_D];
       for (int d = 0; d < HS_D; d++) delta[d] = rows[d];
       store_usage(ka, node, delta, -1);
+      refresh_node_score(ka, node);
     }
     ka.decisions[op] = dec;
     return;
@@ -595,6 +630,7 @@ hs_shard_decide_kernel(const KernelArgs ka, int op) {
       int4 delta[HS_D];
       collapse_rows(ent, la, out.n_alloc, delta);
       store_usage(ka, node, delta, +1);
+      refresh_node_score(ka, node);
       for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)op * HS_D + d] = delta[d];
       dec.status = 0; dec.node = node; dec.score = sc; dec.alloc_off = off; dec.n_alloc = out.n_alloc;
     } else {
@@ -710,7 +746,7 @@ extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int mode, int grid,
   else hs_sweep_kernel<0><<<grid, block, 0, stream>>>(*ka, op);
   return (int)cudaGetLastError();
 }
-extern "C" int hs_sweep_blocks_per_sm(int mode) { return mode == 0 ? 2 : (mode == 1 ? 4 : 6); }
+extern "C" int hs_sweep_blocks_per_sm(int mode) { return mode == 0 ? 2 : (mode == 1 ? 4 : 5); }
 extern "C" int hs_launch_shard_decide(const KernelArgs* ka, int op, cudaStream_t stream) {
   hs_shard_decide_kernel<<<1, 32, 0, stream>>>(*ka, op);
   return (int)cudaGetLastError();

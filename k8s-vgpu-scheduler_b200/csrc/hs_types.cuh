@@ -132,7 +132,7 @@ struct KernelArgs {
   int4* dyn;
   const int4* stat;
   const uint32_t* node_flags;
-  const int4* node_tot;         // per node {flags, sum count, sum totalcore, sum totalmem}
+  int4* node_tot;               // per node {flags, float bits of ComputeDefaultScore on the current usage, 0, 0}: kept current by every commit/release
   const int16_t* pair;          // [node][64]
   int32_t n_nodes;              // slots (padded to HS_TILE)
   // candidate positions: NULL = every alive node, position == slot
