@@ -174,6 +174,7 @@ def run_ours(args):
 
     sampler = ClockSampler(local_rank)
     sampler.start()
+    host0 = e.host_seconds()
     launches0 = e.launch_count()
     dev_ms, e2e_s, fits, nofits, decisions, bytes_alg = [], [], 0, 0, 0, 0
     h2d = d2h = 0
@@ -196,6 +197,8 @@ def run_ours(args):
     torch.cuda.synchronize()
     clocks = sampler.stop()
     launches = e.launch_count() - launches0
+    host1 = e.host_seconds()
+    host_ms = [round(1e3 * (b - a) / args.steps, 3) for a, b in zip(host0, host1)]
 
     total_dev_s = sum(dev_ms) / 1e3
     value = decisions / total_dev_s
@@ -214,7 +217,9 @@ def run_ours(args):
                    "l2": "inventory (%.2f MB) is L2/register resident by design; no flush: each decision depends on the "
                          "previous commit" % (args.nodes * 256 / 1e6)},
         "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": h2d // args.steps,
-                "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": round(1e3 * statistics.mean(e2e_s), 3)},
+                "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": round(1e3 * statistics.mean(e2e_s), 3),
+                "host_ms_per_step": {"compile": host_ms[0], "device_and_copies": host_ms[1], "absorb": host_ms[2],
+                                     "materialise": host_ms[3]}},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
@@ -224,10 +229,28 @@ def run_ours(args):
                              "at 5k nodes the loop is barrier-latency bound, HBM evidence is the scan probe (profiles/)"},
     }
 
+    if not args.no_scan:
+        out["scan_hbm"] = scan_probe(args.scan_nodes, peak)
     if not args.no_cpu:
         out["cpu_baseline"] = cpu_baseline(cfg, nodes, state0, batches[args.warmup], eng, oa, args, local_rank)
     e.close()
     print(json.dumps(out))
+
+
+def scan_probe(n_nodes, peak):
+    """The inventory scan in isolation on an inventory larger than L2: hs_sweep_kernel timed with
+    CUDA events by the hs_scan_probe tool (same library).  algorithmic bytes = nodes x 8 x 32 B."""
+    exe = os.path.join(ROOT, "k8s-vgpu-scheduler_b200", "hs_scan_probe")
+    try:
+        lines = subprocess.run([exe, str(n_nodes)], capture_output=True, text=True, timeout=300).stdout.strip().splitlines()
+        rows = [json.loads(x) for x in lines]
+        best = rows[0]
+        return {"kernel": "hs_sweep_kernel", "nodes": n_nodes, "inventory_mb": best["inventory_mb"], "ms": best["ms"],
+                "achieved": best["algorithmic_gbps"], "peak": peak, "unit": "GB/s", "frac": round(best["algorithmic_gbps"] / peak, 4),
+                "request": best["request"],
+                "numa_bind_variant_gbps": rows[1]["algorithmic_gbps"] if len(rows) > 1 else None}
+    except Exception as ex:  # the probe is an extra; the bench line must still be printed
+        return {"error": str(ex)}
 
 
 def inject_state(target, nodes, state, kind):
@@ -324,6 +347,8 @@ def main():
     ap.add_argument("--fill", type=int, default=FILL_FILTERS)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-scan", action="store_true", help="skip the HBM scan probe")
+    ap.add_argument("--scan-nodes", type=int, default=2000000)
     ap.add_argument("--ref-ops", type=int, default=96, help="ops per step of the --impl reference arm")
     ap.add_argument("--ref-prefill", type=int, default=1500)
     ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c4"], help="diagnostic: another config's stream")

@@ -199,6 +199,8 @@ struct hs_handle {
   std::vector<std::string> modes;
 
   std::vector<NodeSlot> nodes;
+  std::deque<std::string> name_store;      // node names at stable addresses (slot order)
+  std::vector<const char*> name_ptr;       // name_store[slot].c_str()
   std::unordered_map<std::string, int> node_by_name;
   std::unordered_map<std::string, std::vector<uint32_t>> uuid_index;  // uuid -> (slot<<8 | dev)
   int n_alive = 0;
@@ -904,12 +906,18 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
       if (!placed) put_rows();
       std::string& buf = h->r_buf;
       buf.clear();
-      char num[48];
+      auto put_int = [&buf](int v) {   // "%d" without the printf machinery
+        char tmp[12];
+        int n = 0;
+        unsigned u = v < 0 ? 0u - (unsigned)v : (unsigned)v;
+        do { tmp[n++] = (char)('0' + u % 10); u /= 10; } while (u);
+        if (v < 0) buf += '-';
+        while (n) buf += tmp[--n];
+      };
       for (uint32_t i = 0; i < dec.n_alloc; i++) {
         const DevAlloc& a = h->b_alloc.h[dec.alloc_off + i];
-        buf += ns.devs[a.dev].uuid; buf += ','; buf += em.type;
-        snprintf(num, sizeof num, ",%d,%d:", a.usedmem, (int)a.usedcores);
-        buf += num;
+        buf += ns.devs[a.dev].uuid; buf += ','; buf += em.type; buf += ',';
+        put_int(a.usedmem); buf += ','; put_int((int)a.usedcores); buf += ':';
       }
       buf += ';';
       // keys in sorted order: "<vendor>-devices-allocated" < "...-to-allocate" < "hami.io/vgpu-node" < "hami.io/vgpu-time"
@@ -1041,8 +1049,28 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
         else h->r_failed.push_back(hs_failed_node{h->nodes[s].name.c_str(), reason_of(s)});
       }
     } else {
-      for (size_t s = 0; s < h->nodes.size(); s++)
-        if (h->nodes[s].alive) h->r_failed.push_back(hs_failed_node{h->nodes[s].name.c_str(), reason_of((int)s)});
+      // dense walk: names and liveness come from flat arrays (NodeSlot objects are large and scattered), and a run
+      // of nodes with the same 12-byte reason record reuses the string of the previous one
+      const size_t nn = h->nodes.size();
+      h->r_failed.resize(nn);
+      size_t k = 0;
+      if (slot == 0xffffffffu) {
+        for (size_t s = 0; s < nn; s++) if (h->h_flags[s] & NF_ALIVE) h->r_failed[k++] = hs_failed_node{h->name_ptr[s], ""};
+      } else {
+        const DevFail* fr = h->fail_host.data() + (size_t)slot * n_nodes;
+        const char* last = nullptr;
+        uint32_t l0 = 0xffffffffu, l1 = 0, l2 = 0;
+        for (size_t s = 0; s < nn; s++) {
+          if (!(h->h_flags[s] & NF_ALIVE)) continue;
+          const DevFail& f = fr[s];
+          if (!last || f.kind_cards != l0 || f.c0 != l1 || f.c1 != l2) {
+            last = fail_string(h, f).c_str();
+            l0 = f.kind_cards; l1 = f.c0; l2 = f.c1;
+          }
+          h->r_failed[k++] = hs_failed_node{h->name_ptr[s], last};
+        }
+      }
+      h->r_failed.resize(k);
     }
   } else {
     out->status = HS_ERR_CUDA;
@@ -1283,6 +1311,8 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
     if (rc != HS_OK) return rc;
     h->nodes.emplace_back();
     h->nodes[slot].name = node->name;
+    h->name_store.emplace_back(node->name);
+    h->name_ptr.push_back(h->name_store.back().c_str());
     h->node_by_name[node->name] = slot;
   } else {
     slot = it->second;

@@ -175,6 +175,13 @@ class Engine:
             raise RuntimeError("snapshot failed: %d %s" % (n, self.error()))
         return [(rows[i].used, rows[i].usedmem, rows[i].usedcores) for i in range(min(n, cap))]
 
+    def host_seconds(self):
+        """cumulative host seconds: (request compile, device run + copies, absorb, materialise)"""
+        out = (C.c_double * 4)()
+        self.L.hs_debug_host_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        self.L.hs_debug_host_seconds(self.h, out)
+        return [out[i] for i in range(4)]
+
     def last_device_ms(self):
         return self.L.hs_last_device_ms(self.h)
 
