@@ -1,10 +1,13 @@
 """bench.py --gpus N (N > 1): the sharded path of SURVEY §8e on ONE node, one process per GPU (torchrun).
 
 Workload: C5 — a 100,000-node synthetic inventory (C2's device and request mix) partitioned in contiguous
-node blocks across the ranks.  Every rank sees the same pod stream; per decision each rank's sweep kernel
-produces its packed (score, global position) key, an NCCL all-reduce(MAX, uint64) over NVLink merges the
-keys in place, and the rank that owns the winning node commits.  The whole batch is enqueued on the engine's
-stream without host synchronisation; time = CUDA events, MAX over ranks.  scaling: "strong" (the inventory
+node blocks across the ranks.  Every rank sees the same pod stream.  Default (fused): ONE persistent decide
+kernel per GPU runs the whole batch; per decision the CTAs of a GPU combine through the local L2 slot, the
+rank's leader CTA stores the packed (score, global position) key into every peer's mailbox over NVLink
+(peer-mapped memory) and polls its own, and the rank that owns the winning node commits — no launch and no
+library call per decision.  HS_SHARD_NCCL=1 selects the baseline: per decision a sweep kernel, an NCCL
+all-reduce(MAX, uint64) and an owner-commit kernel.  Time = CUDA events, MAX over ranks.
+scaling: "strong" (the inventory
 and the stream are fixed as N grows).
 """
 import json
@@ -50,6 +53,10 @@ def run(args, world, rank, local_rank):
     uid = [eng.unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     e.shard_init(rank, world, uid[0], lo)
+    if world > 1 and not os.environ.get("HS_SHARD_NCCL"):   # fused path: exchange the peer-mailbox IPC handles
+        boxes = [None] * world
+        dist.all_gather_object(boxes, e.shard_mailbox())
+        e.shard_connect(boxes)
 
     cnt, cut = 0, 0
     for i, (k, _) in enumerate(ops):
@@ -92,6 +99,12 @@ def run(args, world, rank, local_rank):
     c = torch.tensor([fits, nofits], dtype=torch.int64, device="cuda")
     dist.all_reduce(c, op=dist.ReduceOp.SUM)
     total_dev_s, total_e2e_s = float(t[0]) / 1e3, float(t[1])
+    fused = world > 1 and not os.environ.get("HS_SHARD_NCCL")
+    mode_desc = ("one persistent decide kernel per GPU; per decision the ranks' leader CTAs exchange the packed arg-best key "
+                 "through peer-mapped mailboxes over NVLink (fused, no launch, no NCCL call)") if fused else \
+                "per decision sweep -> NCCL allreduce(MAX,uint64) -> owner commit (HS_SHARD_NCCL=1 baseline)"
+    mode_note = ("latency-bound: local slot barrier + one NVLink mailbox round trip per decision" if fused
+                 else "latency-bound: 3 kernel launches + one 8-byte NCCL allreduce per decision")
     if rank == 0:
         peak, peak_src = B.measured_peak()
         bytes_alg = decisions * (n_nodes * 8 * 32)
@@ -100,7 +113,7 @@ def run(args, world, rank, local_rank):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * total_dev_s / args.steps, 4),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32+f32", "data": "synthetic",
             "config": {"workload": "C5: %d-node inventory (C2 device/request mix) sharded in contiguous blocks over %d GPUs; "
-                                   "per decision sweep -> NCCL allreduce(MAX,uint64) -> owner commit" % (n_nodes, world),
+                                   "%s" % (n_nodes, world, mode_desc),
                        "ops_per_step": batch, "decisions_timed": decisions, "fits": int(c[0]),
                        "no_fits": int(c[1]) // world, "l2": "each rank's shard (%.1f MB) is L2 resident" % ((hi - lo) * 256 / 1e6)},
             "e2e": {"value": round(decisions / total_e2e_s, 1), "unit": B.UNIT,
@@ -108,8 +121,8 @@ def run(args, world, rank, local_rank):
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": round(bytes_alg / total_dev_s / 1e9, 1), "peak": peak * world,
                          "unit": "GB/s", "frac": round(bytes_alg / total_dev_s / 1e9 / (peak * world), 4), "traffic": None,
-                         "peak_source": peak_src + " x n_gpus", "kernel": "hs_sweep_kernel",
-                         "note": "latency-bound: 3 kernel launches + one 8-byte NCCL allreduce per decision"},
+                         "peak_source": peak_src + " x n_gpus", "kernel": "hs_decide_kernel" if fused else "hs_sweep_kernel",
+                         "note": mode_note},
         }
         print(json.dumps(out))
     e.close()

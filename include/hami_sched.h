@@ -288,6 +288,13 @@ int32_t hs_snapshot_node(hs_handle* h, const char* node, hs_device_usage_row* ro
  * reported as HS_FIT_REMOTE by the others.                                                             */
 int32_t hs_shard_unique_id(void* out128);
 int32_t hs_shard_init(hs_handle* h, int32_t rank, int32_t world, const void* unique_id128, int64_t pos_base);
+/* Fused path: the arg-best merge happens INSIDE the persistent decide kernel over NVLink peer memory (each
+ * rank's leader CTA stores its key into every peer's mailbox and polls its own), so a decision costs no
+ * kernel launch and no NCCL call.  hs_shard_mailbox returns this rank's 64-byte CUDA IPC handle; gather all
+ * ranks' handles (rank order, 64 bytes each) and pass them to hs_shard_connect on every rank.  Up to 8 ranks
+ * on one node.  Without it (or with HS_SHARD_NCCL=1) hs_run_batch uses the NCCL launch-per-decision path.  */
+int32_t hs_shard_mailbox(hs_handle* h, void* out64);
+int32_t hs_shard_connect(hs_handle* h, const void* handles64, int32_t world);
 
 /* ---- the allocation-free entry point (it has no counterpart in the reference) --------------------
  * For callers that cannot call cudaMalloc when they need a scan: a plugin whose device memory is a fixed

@@ -236,6 +236,12 @@ struct hs_handle {
   int shard_rank = 0, shard_world = 1;
   int64_t pos_base = 0;
   void* nccl_comm = nullptr;
+  // fused path: peer-mapped mailboxes (cudaIpc) for the in-kernel arg-best exchange over NVLink
+  unsigned long long* d_mbox = nullptr;       // this rank's mailbox [4 rows][8 ranks] + xresult[4] + xerror
+  unsigned long long* mbox_peer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  bool xgpu_connected = false;
+  bool shard_use_nccl = false;               // HS_SHARD_NCCL=1: keep the launch-per-decision NCCL baseline
+  uint32_t epoch_base = 0;
   bool force_shard = false;  // HS_FORCE_SHARD=1: run the sharded pipeline (sweep / decide / explain kernels) with world == 1
   double host_s[4] = {0, 0, 0, 0};      // diagnostic: cumulative host seconds in compile / device+copies / absorb / summary
   uint32_t fail_cap = 32;
@@ -680,6 +686,12 @@ int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_ca
   ka.counters = h->b_counters.d;
   ka.pos_base = (int32_t)h->pos_base;
   ka.timing = h->timing ? h->b_timing.d : nullptr;
+  ka.world = h->xgpu_connected ? h->shard_world : 1;
+  ka.rank = h->shard_rank;
+  for (int p = 0; p < 8; p++) ka.mbox_peer[p] = h->mbox_peer[p];
+  ka.xresult = h->d_mbox ? h->d_mbox + 32 : nullptr;
+  ka.xerror = h->d_mbox ? reinterpret_cast<uint32_t*>(h->d_mbox + 36) : nullptr;
+  ka.epoch_base = h->epoch_base;
   return HS_OK;
 }
 
@@ -728,6 +740,8 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
     cudaEventElapsedTime(&ms, h->ev0, h->ev1);
     h->last_ms += ms;
     uint32_t ran = h->b_counters.h[2] - (uint32_t)done, nfail = h->b_counters.h[1];
+    h->epoch_base += h->b_counters.h[5];
+    if (h->b_counters.h[6]) { h->err = "fused multi-GPU arg-best: a peer rank never arrived (ranks must submit the same ops)"; return HS_ERR_CUDA; }
     if (nfail) {
       size_t base = h->fail_host.size();
       h->fail_host.resize(base + (size_t)nfail * n_nodes);
@@ -747,7 +761,7 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
     alloc_base = h->b_counters.h[0];
     if (done < n_ops) {
       // resume: keep the alloc cursor, clear the fail cursor
-      h->b_counters.h[1] = 0; h->b_counters.h[2] = 0; h->b_counters.h[3] = 0;
+      h->b_counters.h[1] = 0; h->b_counters.h[2] = 0; h->b_counters.h[3] = 0; h->b_counters.h[5] = 0;
       CUDA_OK(h, cudaMemsetAsync(h->b_best.d + done, 0, sizeof(OpSync), h->stream));  // op `done` runs again
       CUDA_OK(h, cudaMemcpyAsync(h->b_counters.d, h->b_counters.h, 8 * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
@@ -1191,7 +1205,8 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
   if (!uuid_pool.empty()) memcpy(h->b_uuid.h, uuid_pool.data(), uuid_pool.size() * sizeof(uint32_t));
   if (!rel.empty()) memcpy(h->b_rel.h, rel.data(), rel.size() * sizeof(int4));
   const double t1 = now_s();
-  int rc = (h->shard_world > 1 || h->force_shard) ? run_device_ops_sharded(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap)
+  const bool launch_per_op = h->force_shard || (h->shard_world > 1 && (!h->xgpu_connected || h->shard_use_nccl));
+  int rc = launch_per_op ? run_device_ops_sharded(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap)
                               : run_device_ops(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap);
   if (rc != HS_OK) return rc;
   const double t2 = now_s();
@@ -1246,6 +1261,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   if (blk) { int b = atoi(blk); if (b >= 32 && b <= 512 && b % 32 == 0) h->block = b; }
   h->no_fast = getenv("HS_NO_FAST") != nullptr;
   h->force_shard = getenv("HS_FORCE_SHARD") != nullptr;
+  h->shard_use_nccl = getenv("HS_SHARD_NCCL") != nullptr;
   if (getenv("HS_TIMING") && h->b_timing.ensure(16)) { h->timing = true; cudaMemset(h->b_timing.d, 0, 16 * sizeof(unsigned long long)); }
   const char* fc = getenv("HS_FAIL_CAP");
   if (fc && atoi(fc) > 0) h->fail_cap = (uint32_t)atoi(fc);
@@ -1622,6 +1638,36 @@ int32_t hs_shard_init(hs_handle* h, int32_t rank, int32_t world, const void* uni
   memcpy(&id, unique_id128, sizeof id);
   int nr = g_nccl.CommInitRank(&h->nccl_comm, world, id, rank);
   if (nr != 0) { h->err = std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nr) : "?"); return HS_ERR_CUDA; }
+  return HS_OK;
+}
+
+int32_t hs_shard_mailbox(hs_handle* h, void* out64) {
+  if (!h || !out64) return HS_ERR_INVALID;
+  cudaSetDevice(h->device);
+  if (!h->d_mbox) {
+    CUDA_OK(h, cudaMalloc(&h->d_mbox, 64 * sizeof(unsigned long long)));
+    CUDA_OK(h, cudaMemset(h->d_mbox, 0, 64 * sizeof(unsigned long long)));
+  }
+  cudaIpcMemHandle_t mh;
+  CUDA_OK(h, cudaIpcGetMemHandle(&mh, h->d_mbox));
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+  memcpy(out64, &mh, 64);
+  return HS_OK;
+}
+
+int32_t hs_shard_connect(hs_handle* h, const void* handles64, int32_t world) {
+  if (!h || !handles64 || world != h->shard_world || world > 8 || !h->d_mbox) return HS_ERR_INVALID;
+  cudaSetDevice(h->device);
+  for (int p = 0; p < world; p++) {
+    if (p == h->shard_rank) { h->mbox_peer[p] = h->d_mbox; continue; }
+    cudaIpcMemHandle_t mh;
+    memcpy(&mh, (const char*)handles64 + 64 * p, 64);
+    void* ptr = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&ptr, mh, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { h->err = std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e); return HS_ERR_CUDA; }
+    h->mbox_peer[p] = static_cast<unsigned long long*>(ptr);
+  }
+  h->xgpu_connected = true;
   return HS_OK;
 }
 

@@ -128,7 +128,17 @@ __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
 // final.  The launch is cooperative, so every CTA is resident.  Returns the winning key to the CTA.
 // (An all-to-all ring of per-CTA slots polled by a whole warp was measured slower: 157 pollers x 5
 // lines per round hot-spot the L2 slices and delay the arrivals themselves.)
-__device__ __forceinline__ unsigned long long slot_argbest(OpSync* slot, unsigned long long warp_key,
+// Multi-GPU extension (one process per GPU, nodes sharded in contiguous blocks): the CTAs of a GPU first
+// combine through the local slot exactly as above; CTA 0's lane 0 (the rank's leader) then STORES the shard's
+// key, tagged with an 8-bit epoch, into every peer's mailbox over NVLink (peer-mapped memory, one 8-byte
+// relaxed system-scope store per peer: data and arrival in one word), polls its own mailbox until every
+// rank's word carries the epoch, and publishes max(keys) in a local epoch-tagged word that all CTAs of this
+// GPU poll.  The key embeds the GLOBAL position, so max == the canonical arg-best across ranks.  Rows of the
+// mailbox ring are reused 4 barriers later; epochs continue across launches, so nothing is ever reset.
+#define XGPU_SPIN_LIMIT (1u << 24)       // leader: ~10-20 s per peer before it gives up (counters[6] = 1)
+#define XGPU_LOCAL_SPIN_LIMIT (1u << 29)
+__device__ __forceinline__ unsigned long long slot_argbest(const KernelArgs& ka, OpSync* slot, uint32_t b,
+                                                           unsigned long long warp_key,
                                                            unsigned long long* s_red, unsigned long long* s_win) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   if (lane == 0) s_red[warp] = warp_key;
@@ -139,10 +149,43 @@ __device__ __forceinline__ unsigned long long slot_argbest(OpSync* slot, unsigne
     if (lane == 0) {
       if (v) atomicMax(&slot->best, v);
       asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
-      unsigned long long best, cnt;
-      do {
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
-      } while ((uint32_t)cnt < gridDim.x);
+      unsigned long long best = 0, cnt;
+      if (ka.world <= 1) {
+        do {
+          asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
+        } while ((uint32_t)cnt < gridDim.x);
+      } else {
+        const unsigned long long epoch = (unsigned long long)((ka.epoch_base + b + 1u) & 255u);
+        const uint32_t row = (ka.epoch_base + b) & 3u;
+        if (blockIdx.x == 0) {
+          do {
+            asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
+          } while ((uint32_t)cnt < gridDim.x);
+          const unsigned long long mine = (best & ~255ull) | epoch;
+          for (int p = 0; p < ka.world; p++)
+            asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(ka.mbox_peer[p] + row * 8 + ka.rank), "l"(mine) : "memory");
+          unsigned long long g = 0;
+          const unsigned long long* my_box = ka.mbox_peer[ka.rank] + row * 8;
+          for (int p = 0; p < ka.world; p++) {
+            unsigned long long w;
+            uint32_t spins = 0;
+            do {
+              asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(my_box + p) : "memory");
+            } while ((w & 255ull) != epoch && ++spins < XGPU_SPIN_LIMIT);
+            if ((w & 255ull) != epoch) { ka.counters[6] = 1u; w = 0; }
+            g = w > g ? w : g;
+          }
+          asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(ka.xresult + row), "l"((g & ~255ull) | epoch) : "memory");
+          best = g & ~255ull;
+        } else {
+          unsigned long long w;
+          uint32_t spins = 0;
+          do {
+            asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(ka.xresult + row) : "memory");
+          } while ((w & 255ull) != epoch && ++spins < XGPU_LOCAL_SPIN_LIMIT);
+          best = (w & 255ull) == epoch ? (w & ~255ull) : 0ull;
+        }
+      }
       *s_win = best;
     }
   }
@@ -198,6 +241,7 @@ hs_decide_kernel(const KernelArgs ka) {
 
   DevAlloc la[HS_MAX_ALLOC];   // general path (lane 0 of the group): picks of the best owned node for the current op
   uint32_t fail_count = 0;     // no-fit decisions so far: identical in every thread
+  uint32_t barriers = 0;       // arg-best exchanges so far in this launch: identical in every thread (and rank)
   int r = ka.op_begin;
   if (r < ka.n_ops) prefetch_op(ka.pods + r, &s_op[0]);
 
@@ -332,11 +376,25 @@ hs_decide_kernel(const KernelArgs ka) {
     // ---- arg-best: warp shuffle, one atomicMax per CTA, ONE grid barrier -----------------------
     const unsigned long long bk = warp_max_u64(my_key);
     TICK(3);
-    const unsigned long long win = slot_argbest(ka.sync + r, bk, s_red, &s_win);
+    const unsigned long long win = slot_argbest(ka, ka.sync + r, barriers, bk, s_red, &s_win);
+    barriers++;
     TICK(4);
 
     if (KEY_VALID(win)) {
       const bool mine = my_key == win;   // uniform within the group
+      if (ka.world > 1 && gtid == 0) {
+        const int lp = KEY_POS(win) - ka.pos_base;
+        if (lp < 0 || lp >= ka.n_nodes) {     // the winner lives on another rank's shard
+          DevDecision dec;
+          dec.status = 3; dec.node = KEY_POS(win); dec.alloc_off = 0; dec.n_alloc = 0; dec.fail_slot = 0xffffffffu;
+          uint32_t u = (uint32_t)(win >> 32);
+          if (spread) u = ~u;
+          u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+          dec.score = __uint_as_float(u);
+          dec.pad[0] = dec.pad[1] = 0;
+          ka.decisions[r] = dec;
+        }
+      }
       if (fast) {
         if ((lite || !resident) && __any_sync(FULL, mine)) {
           // the sweep only established THAT the node fits (or ran on streamed registers): the winner's warp
@@ -449,7 +507,7 @@ hs_decide_kernel(const KernelArgs ka) {
     my_pre = fast_node_score(D);
     if ((dirty || reload) && glane == 0 && gg < ka.n_nodes) ka.node_tot[gg].y = __float_as_int(my_pre);
   }
-  if (gtid == 0) { ka.counters[2] = (uint32_t)r; ka.counters[1] = fail_count; }
+  if (gtid == 0) { ka.counters[2] = (uint32_t)r; ka.counters[1] = fail_count; ka.counters[5] = barriers; }
 }
 
 // Sweep-only kernel: evaluates ONE request against the whole inventory and reduces to the arg-best key

@@ -155,5 +155,12 @@ struct KernelArgs {
   uint32_t* counters;           // [0] alloc cursor, [1] fail cursor, [2] ops completed, [3] barrier arrive, [4] barrier epoch
   // multi-GPU: global position of this shard's slot 0 (argbest key carries global positions)
   int32_t pos_base;
+  // fused multi-GPU arg-best (peer memory over NVLink): every rank's leader CTA stores its shard's key into each
+  // peer's mailbox and polls its own; see xgpu_argbest in hs_kernels.cu.  world <= 1: unused.
+  int32_t world, rank;
+  unsigned long long* mbox_peer[8];   // mbox_peer[p] = rank p's mailbox, mapped into this process: [4 rows][8 ranks]
+  unsigned long long* xresult;        // local: [4] epoch-tagged global winner, polled by every CTA of this GPU
+  uint32_t epoch_base;                // barriers executed by earlier launches of this handle (epochs never restart)
+  uint32_t* xerror;                   // set to 1 if a peer never arrived (bounded spin)
   unsigned long long* timing;   // diagnostic: 8 phase-clock accumulators written by block 0 (NULL = off)
 };

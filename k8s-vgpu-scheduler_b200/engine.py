@@ -18,7 +18,7 @@ EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_batch_get", "hs_rollback",
     "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
-    "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
+    "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
 ]
 
 
@@ -167,6 +167,18 @@ class Engine:
         """unique_id: 128 bytes from unique_id() on rank 0 (None when world == 1)."""
         buf = C.create_string_buffer(bytes(unique_id), 128) if unique_id is not None else None
         return self._check(self.L.hs_shard_init(self.h, rank, world, buf, pos_base))
+
+    def shard_mailbox(self):
+        buf = C.create_string_buffer(64)
+        self.L.hs_shard_mailbox.argtypes = [C.c_void_p, C.c_void_p]
+        self._check(self.L.hs_shard_mailbox(self.h, buf))
+        return buf.raw
+
+    def shard_connect(self, handles):
+        """handles: list of every rank's 64-byte mailbox handle, in rank order."""
+        blob = C.create_string_buffer(b"".join(handles), 64 * len(handles))
+        self.L.hs_shard_connect.argtypes = [C.c_void_p, C.c_void_p, C.c_int32]
+        return self._check(self.L.hs_shard_connect(self.h, blob, len(handles)))
 
     def snapshot(self, node, cap=16):
         rows = (abi.hs_device_usage_row * cap)()

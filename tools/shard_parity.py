@@ -37,6 +37,10 @@ def main():
         uid = [eng.unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         e.shard_init(rank, world, uid[0], lo)
+        if world > 1 and not os.environ.get("HS_SHARD_NCCL"):   # fused path: exchange the peer-mailbox IPC handles
+            boxes = [None] * world
+            dist.all_gather_object(boxes, e.shard_mailbox())
+            e.shard_connect(boxes)
         got = []
         for s in range(0, len(ops), 500):
             part = ops[s:s + 500]
