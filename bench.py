@@ -147,7 +147,7 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1 or args.gpus > 1:
+    if world > 1 or args.gpus > 1 or args.workload == "c5":
         import bench_multi
         return bench_multi.run(args, world, rank, local_rank)
     if not torch.cuda.is_available():
@@ -351,7 +351,8 @@ def main():
     ap.add_argument("--scan-nodes", type=int, default=2000000)
     ap.add_argument("--ref-ops", type=int, default=96, help="ops per step of the --impl reference arm")
     ap.add_argument("--ref-prefill", type=int, default=1500)
-    ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c4"], help="diagnostic: another config's stream")
+    ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c4", "c5"],
+                    help="diagnostic: another config's stream (c5 = the multi-GPU workload, runnable on 1 GPU for the scaling base)")
     args = ap.parse_args()
     global WORKLOAD
     WORKLOAD = args.workload

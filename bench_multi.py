@@ -39,6 +39,11 @@ def run(args, world, rank, local_rank):
 
     if world != args.gpus:
         raise SystemExit("launch with torchrun --nproc-per-node %d" % args.gpus)
+    if world == 1:   # plain `python bench.py --workload c5`: a one-rank group
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29533")
+        os.environ.setdefault("RANK", "0")
+        os.environ.setdefault("WORLD_SIZE", "1")
     torch.cuda.set_device(local_rank)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_nodes = args.nodes if args.nodes != B.N_NODES else N_NODES

@@ -329,20 +329,38 @@ hs_decide_kernel(const KernelArgs ka) {
           my_node = gg;
         }
       } else {
+        // streaming: the shard does not fit the grid's registers.  Software pipeline as in hs_sweep_kernel: the next
+        // node's three 16 B loads are in flight while this node is evaluated; the node score is the cached
+        // ComputeDefaultScore in node_tot (every commit/release in this mode refreshes it before the next op).
         DevRegs n;
         FastEval f2;
-        for (int node = gg; node < ka.n_nodes; node += ngroups) {   // n_nodes % 32 == 0: warp-uniform trip count
-          const uint32_t nf = ka.node_flags[node];
+        int node = gg;
+        int4 nt = make_int4(0, 0, 0, 0), a = nt, b = nt;
+        if (node < ka.n_nodes) {
+          nt = ka.node_tot[node];
+          a = ka.dyn[(size_t)node * HS_D + glane];
+          b = __ldg(ka.stat + (size_t)node * HS_D + glane);
+        }
+        while (node < ka.n_nodes) {   // n_nodes % 32 == 0: warp-uniform trip count
+          const int next = node + ngroups;
+          int4 nt2 = make_int4(0, 0, 0, 0), a2 = nt2, b2 = nt2;
+          if (next < ka.n_nodes) {
+            nt2 = ka.node_tot[next];
+            a2 = ka.dyn[(size_t)next * HS_D + glane];
+            b2 = __ldg(ka.stat + (size_t)next * HS_D + glane);
+          }
+          const uint32_t nf = (uint32_t)nt.x;
           const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
-          load_dev(ka, node, glane, n);
+          n.used = a.x; n.mem = a.y; n.cores = a.z; n.dflags = (uint32_t)a.w;
+          n.count = b.x; n.totmem = b.y; n.totcore = b.z; n.packed = (uint32_t)b.w;
           const bool fit = (lite ? fast_fit_lite(n, glane, gbase, (uint32_t)node, nf, pod, pod.e0, ka)
                                  : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, f2)) && pos >= 0;
-          if (!__any_sync(FULL, fit)) continue;          // warp-uniform: the node score is a quarter-warp collective
-          const float sc = fast_node_score(n);
           if (fit) {
+            const float sc = __int_as_float(nt.y);
             const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
             if (key > my_key) { my_key = key; my_node = node; my_score = sc; }
           }
+          node = next; nt = nt2; a = a2; b = b2;
         }
       }
     } else {
