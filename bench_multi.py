@@ -110,6 +110,25 @@ def run(args, world, rank, local_rank):
                 "per decision sweep -> NCCL allreduce(MAX,uint64) -> owner commit (HS_SHARD_NCCL=1 baseline)"
     mode_note = ("latency-bound: local slot barrier + one NVLink mailbox round trip per decision" if fused
                  else "latency-bound: 3 kernel launches + one 8-byte NCCL allreduce per decision")
+    # the scaling base: the SAME inventory and the same batches on ONE GPU (rank 0, unsharded engine), so the line
+    # carries its own 1-GPU number for this workload (bench.py --gpus 1 runs C3, the metric's config)
+    single = None
+    if world > 1 and rank == 0 and not os.environ.get("HS_NO_SINGLE"):
+        e1 = eng.Engine(cfg["node_policy"], cfg["gpu_policy"], cuda_device=local_rank, reserve_nodes=n_nodes)
+        for n in nodes:
+            e1.node_upsert(n)
+        e1.run_batch(eng.PackedOps(fill))
+        for i in range(args.warmup):
+            e1.run_batch(packed[i])
+        ms1 = 0.0
+        for i in range(args.warmup, args.warmup + args.steps):
+            e1.run_batch(packed[i])
+            ms1 += e1.last_device_ms()
+        single = {"value": round(decisions / (ms1 / 1e3), 1), "unit": B.UNIT, "n_gpus": 1,
+                  "ms_per_step": round(ms1 / args.steps, 4), "what": "same inventory and batches, unsharded, on rank 0's GPU"}
+        e1.close()
+    if world > 1:
+        dist.barrier()
     if rank == 0:
         peak, peak_src = B.measured_peak()
         bytes_alg = decisions * (n_nodes * 8 * 32)
@@ -123,7 +142,7 @@ def run(args, world, rank, local_rank):
                        "no_fits": int(c[1]) // world, "l2": "each rank's shard (%.1f MB) is L2 resident" % ((hi - lo) * 256 / 1e6)},
             "e2e": {"value": round(decisions / total_e2e_s, 1), "unit": B.UNIT,
                     "h2d_bytes_per_step": batch * 160, "d2h_bytes_per_step": batch * 160},
-            "gpu_launches": int(launches), "clocks": clocks,
+            "gpu_launches": int(launches), "clocks": clocks, "single_gpu_same_workload": single,
             "roofline": {"bound": "hbm", "achieved": round(bytes_alg / total_dev_s / 1e9, 1), "peak": peak * world,
                          "unit": "GB/s", "frac": round(bytes_alg / total_dev_s / 1e9 / (peak * world), 4), "traffic": None,
                          "peak_source": peak_src + " x n_gpus", "kernel": "hs_decide_kernel" if fused else "hs_sweep_kernel",

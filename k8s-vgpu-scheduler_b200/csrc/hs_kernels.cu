@@ -131,12 +131,11 @@ __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
 // Multi-GPU extension (one process per GPU, nodes sharded in contiguous blocks): the CTAs of a GPU first
 // combine through the local slot exactly as above; CTA 0's lane 0 (the rank's leader) then STORES the shard's
 // key, tagged with an 8-bit epoch, into every peer's mailbox over NVLink (peer-mapped memory, one 8-byte
-// relaxed system-scope store per peer: data and arrival in one word), polls its own mailbox until every
-// rank's word carries the epoch, and publishes max(keys) in a local epoch-tagged word that all CTAs of this
-// GPU poll.  The key embeds the GLOBAL position, so max == the canonical arg-best across ranks.  Rows of the
+// relaxed system-scope store per peer: data and arrival in one word).  Warp 0 of EVERY CTA polls this GPU's own
+// mailbox row (lane p watches rank p's word) until every word carries the epoch and takes the max — there is no
+// second publish hop.  The key embeds the GLOBAL position, so max == the canonical arg-best across ranks.  Rows of the
 // mailbox ring are reused 4 barriers later; epochs continue across launches, so nothing is ever reset.
-#define XGPU_SPIN_LIMIT (1u << 24)       // leader: ~10-20 s per peer before it gives up (counters[6] = 1)
-#define XGPU_LOCAL_SPIN_LIMIT (1u << 29)
+#define XGPU_SPIN_LIMIT (1u << 24)       // ~10-20 s of polling before a CTA gives up on a peer (counters[6] = 1)
 __device__ __forceinline__ unsigned long long slot_argbest(const KernelArgs& ka, OpSync* slot, uint32_t b,
                                                            unsigned long long warp_key,
                                                            unsigned long long* s_red, unsigned long long* s_win) {
@@ -146,47 +145,47 @@ __device__ __forceinline__ unsigned long long slot_argbest(const KernelArgs& ka,
   if (warp == 0) {
     unsigned long long v = lane < nwarps ? s_red[lane] : 0ull;
     v = warp_max_u64(v);
-    if (lane == 0) {
-      if (v) atomicMax(&slot->best, v);
-      asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
-      unsigned long long best = 0, cnt;
-      if (ka.world <= 1) {
+    if (ka.world <= 1) {
+      if (lane == 0) {
+        if (v) atomicMax(&slot->best, v);
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
+        unsigned long long best = 0, cnt;
         do {
           asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
         } while ((uint32_t)cnt < gridDim.x);
-      } else {
-        const unsigned long long epoch = (unsigned long long)((ka.epoch_base + b + 1u) & 255u);
-        const uint32_t row = (ka.epoch_base + b) & 3u;
-        if (blockIdx.x == 0) {
+        *s_win = best;
+      }
+    } else {
+      const unsigned long long epoch = (unsigned long long)((ka.epoch_base + b + 1u) & 255u);
+      const uint32_t row = (ka.epoch_base + b) & 3u;
+      if (lane == 0) {
+        if (v) atomicMax(&slot->best, v);
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
+        if (blockIdx.x == 0) {      // the rank's leader: wait for this GPU's CTAs, then post the shard's key to every rank
+          unsigned long long best = 0, cnt;
           do {
             asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
           } while ((uint32_t)cnt < gridDim.x);
           const unsigned long long mine = (best & ~255ull) | epoch;
-          for (int p = 0; p < ka.world; p++)
-            asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(ka.mbox_peer[p] + row * 8 + ka.rank), "l"(mine) : "memory");
-          unsigned long long g = 0;
-          const unsigned long long* my_box = ka.mbox_peer[ka.rank] + row * 8;
-          for (int p = 0; p < ka.world; p++) {
-            unsigned long long w;
-            uint32_t spins = 0;
-            do {
-              asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(my_box + p) : "memory");
-            } while ((w & 255ull) != epoch && ++spins < XGPU_SPIN_LIMIT);
-            if ((w & 255ull) != epoch) { ka.counters[6] = 1u; w = 0; }
-            g = w > g ? w : g;
+          for (int p = 1; p <= ka.world; p++) {     // peers first, own mailbox last
+            const int q = (ka.rank + p) % ka.world;
+            asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(ka.mbox_peer[q] + row * 8 + ka.rank), "l"(mine) : "memory");
           }
-          asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(ka.xresult + row), "l"((g & ~255ull) | epoch) : "memory");
-          best = g & ~255ull;
-        } else {
-          unsigned long long w;
-          uint32_t spins = 0;
-          do {
-            asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(ka.xresult + row) : "memory");
-          } while ((w & 255ull) != epoch && ++spins < XGPU_LOCAL_SPIN_LIMIT);
-          best = (w & 255ull) == epoch ? (w & ~255ull) : 0ull;
         }
       }
-      *s_win = best;
+      // every CTA polls this GPU's own mailbox row (lane p watches rank p's word): no second publish hop
+      const unsigned long long* my_box = ka.mbox_peer[ka.rank] + row * 8;
+      unsigned long long w = epoch;
+      uint32_t spins = 0;
+      bool ok;
+      do {
+        if (lane < ka.world) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(my_box + lane) : "memory");
+        ok = __all_sync(0xffffffffu, (w & 255ull) == epoch);
+      } while (!ok && ++spins < XGPU_SPIN_LIMIT);
+      if (!ok) { if (lane == 0) ka.counters[6] = 1u; w = 0; }
+      w = lane < ka.world ? (w & ~255ull) : 0ull;
+      w = warp_max_u64(w);
+      if (lane == 0) *s_win = w;
     }
   }
   __syncthreads();
