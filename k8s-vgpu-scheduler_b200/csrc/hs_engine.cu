@@ -243,6 +243,11 @@ struct hs_handle {
   bool shard_use_nccl = false;               // HS_SHARD_NCCL=1: keep the launch-per-decision NCCL baseline
   uint32_t epoch_base = 0;
   bool force_shard = false;  // HS_FORCE_SHARD=1: run the sharded pipeline (sweep / decide / explain kernels) with world == 1
+  struct FailTab { uint32_t k0, k1, k2; const std::string* s; };
+  static constexpr uint32_t kFailTab = 8192;
+  std::vector<FailTab> fail_tab = std::vector<FailTab>(kFailTab, FailTab{0, 0, 0, nullptr});
+  bool hostprof = false;                // HS_HOSTPROF=1: split the summary time by result kind, printed at hs_destroy
+  double prof_s[4] = {0, 0, 0, 0};      // fit / no-fit / other / count
   double host_s[4] = {0, 0, 0, 0};      // diagnostic: cumulative host seconds in compile / device+copies / absorb / summary
   uint32_t fail_cap = 32;
   std::vector<OpMeta> metas;            // per device op
@@ -641,12 +646,13 @@ std::string encode_pod_single(const std::vector<std::vector<const hs_alloc_entry
 
 const std::string& fail_string_slow(hs_handle* h, const DevFail& f);
 inline const std::string& fail_string(hs_handle* h, const DevFail& f) {
-  // neighbouring nodes usually fail for the same reason: one-entry cache in front of the map
-  if (h->last_fail_str && f.kind_cards == h->last_fail.kind_cards && f.c0 == h->last_fail.c0 && f.c1 == h->last_fail.c1)
-    return *h->last_fail_str;
+  // a no-fit result names every node; at ~70 % occupancy neighbouring nodes differ, so the lookup runs once per
+  // node: a direct-mapped table of reason records in front of the map (references into the map stay valid)
+  const uint32_t hsh = (f.kind_cards * 0x9E3779B1u) ^ (f.c0 * 0x85EBCA6Bu) ^ (f.c1 * 0xC2B2AE35u);
+  hs_handle::FailTab& t = h->fail_tab[(hsh >> 16) & (hs_handle::kFailTab - 1)];
+  if (t.s && t.k0 == f.kind_cards && t.k1 == f.c0 && t.k2 == f.c1) return *t.s;
   const std::string& s = fail_string_slow(h, f);
-  h->last_fail = f;
-  h->last_fail_str = &s;
+  t.k0 = f.kind_cards; t.k1 = f.c0; t.k2 = f.c1; t.s = &s;
   return s;
 }
 const std::string& fail_string_slow(hs_handle* h, const DevFail& f) {
@@ -1262,6 +1268,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   h->no_fast = getenv("HS_NO_FAST") != nullptr;
   h->force_shard = getenv("HS_FORCE_SHARD") != nullptr;
   h->shard_use_nccl = getenv("HS_SHARD_NCCL") != nullptr;
+  h->hostprof = getenv("HS_HOSTPROF") != nullptr;
   if (getenv("HS_TIMING") && h->b_timing.ensure(16)) { h->timing = true; cudaMemset(h->b_timing.d, 0, 16 * sizeof(unsigned long long)); }
   const char* fc = getenv("HS_FAIL_CAP");
   if (fc && atoi(fc) > 0) h->fail_cap = (uint32_t)atoi(fc);
@@ -1274,6 +1281,9 @@ hs_handle* hs_create(const hs_config* cfg) {
 }
 
 void hs_destroy(hs_handle* h) {
+  if (h && h->hostprof)
+    fprintf(stderr, "[hs hostprof] summary: fit %.3f ms, no-fit %.3f ms, other %.3f ms over %.0f results\n", 1e3 * h->prof_s[0],
+            1e3 * h->prof_s[1], 1e3 * h->prof_s[2], h->prof_s[3]);
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->d_dyn) { cudaFree(h->d_dyn); cudaFree(h->d_stat); cudaFree(h->d_flags); cudaFree(h->d_pair); }
@@ -1530,7 +1540,12 @@ int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint6
     memset(&r, 0, sizeof r);
     if (h->user_status[i] != HS_OK) r.status = h->user_status[i];
     else if (h->user_first_op[i] < 0) r.status = HS_ERR_INVALID;
-    else assemble_result(h, h->user_first_op[i], &r);
+    else if (h->hostprof) {
+      const double a0 = now_s();
+      assemble_result(h, h->user_first_op[i], &r);
+      h->prof_s[r.status == HS_FIT ? 0 : (r.status == HS_NOFIT ? 1 : 2)] += now_s() - a0;
+      h->prof_s[3] += 1;
+    } else assemble_result(h, h->user_first_op[i], &r);
     int32_t st = r.status;
     if (!digest) {   // materialise only: count, do not hash
       if (h->user_first_op[i] >= 0 && h->metas[h->user_first_op[i]].kind == OP_FILTER) { if (st == HS_FIT) fit++; else if (st == HS_NOFIT) nofit++; }
