@@ -296,6 +296,63 @@ int32_t hs_shard_init(hs_handle* h, int32_t rank, int32_t world, const void* uni
 int32_t hs_shard_mailbox(hs_handle* h, void* out64);
 int32_t hs_shard_connect(hs_handle* h, const void* handles64, int32_t world);
 
+/* ---- ingest: the data formats that keep the HBM inventory true ---------------------------
+ * The reference learns a node's devices from register annotations and a pod's committed allocation from its
+ * "<vendor>-devices-allocated" annotations; these entry points take the annotation STRINGS.                */
+enum { HS_REG_CSV = 0,    /* device.DecodeNodeDevices  (pkg/device/devices.go:317-381): DCU, iluvatar      */
+       HS_REG_JSON = 1 }; /* device.UnMarshalNodeDevices (pkg/device/devices.go:445-449): NVIDIA, Ascend, … */
+
+typedef struct hs_vendor_registration {
+  const char* vendor;       /* CommonWord(); becomes DeviceInfo.DeviceVendor of every decoded device          */
+  int32_t     format;       /* HS_REG_*                                                                      */
+  const char* annotation;   /* value of the vendor's node register annotation (e.g. hami.io/node-nvidia-register) */
+  const char* pair_scores;  /* value of hami.io/node-nvidia-score, NULL = absent (nvidia/device.go:319-340)   */
+} hs_vendor_registration;
+
+/* One ContainerDevice of a decoded / collapsed PodDevices (devices.go:205-216): uuid NULL marks an EMPTY
+ * container at (key, container) — DecodePodDevices keeps those to preserve the container index mapping.    */
+typedef struct hs_pod_device {
+  const char* key;          /* PodDevices map key (the vendor word of the checklist)                         */
+  uint32_t    container;
+  const char* uuid;
+  const char* type;
+  int32_t     usedmem;
+  int32_t     usedcores;
+  int32_t     slots;        /* 0 in raw decoded entries; set by the collapse functions                       */
+} hs_pod_device;
+
+/* <vendor>.GetNodeDevices without the node object (nvidia/device.go:302-345, hygon/device.go:131-151,
+ * ascend/device.go:197-215): decode one vendor's register annotation (+ pair scores).  Pure host code, needs no
+ * handle and no GPU.  Outputs point into thread-local storage, valid until the next hs_decode_* call on this
+ * thread.  *pair_scores is row-major n x n (NULL when reg->pair_scores is NULL).  Errors: HS_ERR_INVALID with the
+ * reference's error text in hs_last_error(NULL); an empty device list is HS_ERR_NOTFOUND ("no gpu found on node"). */
+int32_t hs_decode_node_devices(const hs_vendor_registration* reg, const hs_device_info** devices, uint32_t* n_devices,
+                               const int32_t** pair_scores);
+/* device.DecodePodDevices (devices.go:526-556): checklist = (PodDevices key, annotation name) pairs, e.g.
+ * SupportDevices {"NVIDIA": "hami.io/vgpu-devices-allocated"}.  Entries sorted by key, then container.      */
+int32_t hs_decode_pod_devices(const hs_kv* checklist, uint32_t n_checklist, const hs_kv* annotations, uint32_t n_annotations,
+                              const hs_pod_device** devices, uint32_t* n_devices);
+/* mode 0: device.CollapseInitContainerUsage (initContainer.go:36-114); 1: AppContainersOnlyDeviceUsage (:118-157).
+ * Output per key: container 0, devices sorted by UUID, slots set.                                            */
+int32_t hs_collapse_pod_devices(int32_t mode, uint32_t n_init, const hs_pod_device* raw, uint32_t n_raw,
+                                const hs_pod_device** devices, uint32_t* n_devices);
+
+/* One node of the register loop (scheduler.go:469-533, health handshake excluded): decode every vendor's
+ * annotation, skip vendors that fail to decode or report no device, and upsert the node with the devices that
+ * remain (vendors in sorted key order, registration order inside a vendor).  No device left = the node is
+ * removed (rmNodeDevices).  Returns the number of devices registered, or a negative status.                 */
+int32_t hs_node_register(hs_handle* h, const char* node, const hs_vendor_registration* regs, uint32_t n_regs,
+                         const char* device_cordon, int8_t hami_vnpu_core);
+/* onAddPod (scheduler.go:137-171) / restart replay: DecodePodDevices over the registered vendors'
+ * "*-devices-allocated" annotations, CollapseInitContainerUsage, podManager.AddPod (pods.go:57-97: an existing
+ * pod's devices are replaced unless its init-container share was already released).  `node` = the value of
+ * hami.io/vgpu-node; it must be registered (HS_ERR_NOTFOUND otherwise: ingest nodes first).                  */
+int32_t hs_pod_ingest(hs_handle* h, const char* pod_uid, const char* node, const hs_kv* annotations, uint32_t n_annotations,
+                      uint32_t n_init);
+/* onUpdatePod once every init container has succeeded (scheduler.go:200-222): usage shrinks to
+ * AppContainersOnlyDeviceUsage, once (podManager.UpdatePodDevice).                                           */
+int32_t hs_pod_shrink(hs_handle* h, const char* pod_uid, const hs_kv* annotations, uint32_t n_annotations, uint32_t n_init);
+
 /* ---- the allocation-free entry point (it has no counterpart in the reference) --------------------
  * For callers that cannot call cudaMalloc when they need a scan: a plugin whose device memory is a fixed
  * pool carved up at start-up, or a latency-critical path that must not enter the driver's allocator.

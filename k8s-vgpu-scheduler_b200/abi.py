@@ -29,6 +29,18 @@ class hs_node_info(C.Structure):
                 ("pair_scores", C.POINTER(C.c_int32)), ("device_cordon", C.c_char_p), ("hami_vnpu_core", C.c_int8)]
 
 
+class hs_vendor_registration(C.Structure):
+    _fields_ = [("vendor", C.c_char_p), ("format", C.c_int32), ("annotation", C.c_char_p), ("pair_scores", C.c_char_p)]
+
+
+class hs_pod_device(C.Structure):
+    _fields_ = [("key", C.c_char_p), ("container", C.c_uint32), ("uuid", C.c_char_p), ("type", C.c_char_p),
+                ("usedmem", C.c_int32), ("usedcores", C.c_int32), ("slots", C.c_int32)]
+
+
+HS_REG_CSV, HS_REG_JSON = 0, 1
+
+
 class hs_container_request(C.Structure):
     _fields_ = [("key", C.c_char_p), ("type", C.c_char_p), ("nums", C.c_int32), ("memreq", C.c_int32),
                 ("mempct", C.c_int32), ("coresreq", C.c_int32)]

@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "../../include/hami_sched.h"
+#include "hs_ingest.h"
 #include "hs_types.cuh"
 
 extern "C" int hs_launch_decide(const KernelArgs* ka, int grid, int block, cudaStream_t stream);
@@ -140,6 +141,7 @@ struct VendorInfo {
 struct PodRec {           // podManager entry: what to subtract when the pod goes away
   int node;
   int4 delta[HS_D];
+  bool init_released = false;   // PodInfo.InitContainerResourceReleased (pods.go:40-53)
 };
 
 struct EntryMeta {
@@ -1722,6 +1724,8 @@ double hs_last_device_ms(const hs_handle* h) { return h ? h->last_ms : 0.0; }
 uint64_t hs_launch_count(const hs_handle* h) { return h ? h->launches : 0; }
 
 }  // extern "C"
+
+#include "hs_ingest_abi.inc"
 
 // ================================================================================================
 // hs_sweep_static — the one entry point of this library that allocates NOTHING.

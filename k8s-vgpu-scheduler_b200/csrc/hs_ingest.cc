@@ -1,0 +1,488 @@
+// hs_ingest.cc — the data formats on the INPUT side of the hot path: the node register
+// annotations that describe a node's devices and the pod annotations that record a committed allocation.
+// Plain host C++ (no CUDA); the entry points that change the HBM inventory (hs_node_register, hs_pod_ingest,
+// hs_pod_shrink) live in hs_engine.cu and call the decoders here.
+//
+//   decode_node_csv     device.DecodeNodeDevices      pkg/device/devices.go:317-381   (DCU, iluvatar: "id,count,mem,core,type,numa,health[,index,mode]:")
+//   decode_node_json    device.UnMarshalNodeDevices   pkg/device/devices.go:445-449   (NVIDIA, Ascend, …: JSON array of DeviceInfo, tags devices.go:128-140)
+//   decode_pair_scores  device.DecodePairScores       pkg/device/devices.go:383-389 + the fit loop nvidia/device.go:319-340
+//   decode_pod_devices  device.DecodePodDevices       pkg/device/devices.go:526-556 (+ DecodeContainerDevices :496-524)
+//   collapse            device.CollapseInitContainerUsage / AppContainersOnlyDeviceUsage   pkg/device/initContainer.go:36-157
+#include "hs_ingest.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <memory>
+
+namespace hs_ingest {
+namespace {
+
+// ---- strconv look-alikes: same accept/reject set and the same error text as Go's ----------------------
+bool all_digits(const std::string& s, size_t from) {
+  if (from >= s.size()) return false;
+  for (size_t i = from; i < s.size(); i++)
+    if (s[i] < '0' || s[i] > '9') return false;
+  return true;
+}
+std::string quote(const std::string& s) {   // strconv.Quote for the plain-ASCII strings that occur here
+  std::string o = "\"";
+  for (char c : s) {
+    if (c == '"' || c == '\\') { o += '\\'; o += c; }
+    else if (c == '\n') o += "\\n";
+    else if (c == '\t') o += "\\t";
+    else if (c == '\r') o += "\\r";
+    else o += c;
+  }
+  return o + "\"";
+}
+// strconv.ParseInt(s, 10, bits) / strconv.Atoi (fn names the function in the error, Atoi parses as int64)
+bool parse_int(const std::string& s, int bits, const char* fn, int64_t& out, std::string& err) {
+  size_t i = (!s.empty() && (s[0] == '+' || s[0] == '-')) ? 1 : 0;
+  if (!all_digits(s, i)) { err = std::string("strconv.") + fn + ": parsing " + quote(s) + ": invalid syntax"; return false; }
+  const bool neg = s[0] == '-';
+  unsigned long long v = 0;
+  bool over = false;
+  for (; i < s.size(); i++) {
+    if (v > (~0ull - 9) / 10) { over = true; break; }
+    v = v * 10 + (unsigned)(s[i] - '0');
+  }
+  const unsigned long long lim = 1ull << (bits - 1);
+  if (over || (neg ? v > lim : v > lim - 1)) { err = std::string("strconv.") + fn + ": parsing " + quote(s) + ": value out of range"; return false; }
+  out = neg ? -(int64_t)v : (int64_t)v;
+  return true;
+}
+bool parse_bool(const std::string& s, bool& out, std::string& err) {
+  static const char* t[] = {"1", "t", "T", "TRUE", "true", "True"};
+  static const char* f[] = {"0", "f", "F", "FALSE", "false", "False"};
+  for (auto x : t) if (s == x) { out = true; return true; }
+  for (auto x : f) if (s == x) { out = false; return true; }
+  err = "strconv.ParseBool: parsing " + quote(s) + ": invalid syntax";
+  return false;
+}
+std::vector<std::string> split(const std::string& s, char sep) {   // strings.Split
+  std::vector<std::string> out;
+  size_t b = 0;
+  for (;;) {
+    size_t e = s.find(sep, b);
+    if (e == std::string::npos) { out.push_back(s.substr(b)); break; }
+    out.push_back(s.substr(b, e - b));
+    b = e + 1;
+  }
+  return out;
+}
+
+// ---- a small strict JSON reader (RFC 8259) --------------------------------------------------------------
+
+struct JV {
+  enum Kind { Null, Bool, Num, Str, Arr, Obj } kind = Null;
+  bool b = false;
+  std::string s;                                   // Str: decoded text; Num: the literal as written
+  std::vector<JV> a;
+  std::vector<std::pair<std::string, JV>> o;       // members in document order (a later duplicate wins, like Go)
+};
+
+struct JParser {
+  const std::string& t;
+  size_t i = 0;
+  std::string err;
+  int depth = 0;
+  explicit JParser(const std::string& text) : t(text) {}
+  void ws() { while (i < t.size() && (t[i] == ' ' || t[i] == '\t' || t[i] == '\n' || t[i] == '\r')) i++; }
+  bool fail(const std::string& m) { if (err.empty()) err = m; return false; }
+  bool lit(const char* w) {
+    size_t n = strlen(w);
+    if (t.compare(i, n, w) != 0) return fail(std::string("invalid character near offset ") + std::to_string(i));
+    i += n;
+    return true;
+  }
+  static void utf8(std::string& o, uint32_t c) {
+    if (c < 0x80) o += (char)c;
+    else if (c < 0x800) { o += (char)(0xC0 | (c >> 6)); o += (char)(0x80 | (c & 63)); }
+    else if (c < 0x10000) { o += (char)(0xE0 | (c >> 12)); o += (char)(0x80 | ((c >> 6) & 63)); o += (char)(0x80 | (c & 63)); }
+    else { o += (char)(0xF0 | (c >> 18)); o += (char)(0x80 | ((c >> 12) & 63)); o += (char)(0x80 | ((c >> 6) & 63)); o += (char)(0x80 | (c & 63)); }
+  }
+  bool hex4(uint32_t& v) {
+    if (i + 4 > t.size()) return fail("unexpected end of JSON input");
+    v = 0;
+    for (int k = 0; k < 4; k++) {
+      char c = t[i++];
+      v <<= 4;
+      if (c >= '0' && c <= '9') v |= (uint32_t)(c - '0');
+      else if (c >= 'a' && c <= 'f') v |= (uint32_t)(c - 'a' + 10);
+      else if (c >= 'A' && c <= 'F') v |= (uint32_t)(c - 'A' + 10);
+      else return fail("invalid character in \\u escape");
+    }
+    return true;
+  }
+  bool str(std::string& out) {
+    i++;  // opening quote
+    for (;;) {
+      if (i >= t.size()) return fail("unexpected end of JSON input");
+      unsigned char c = (unsigned char)t[i++];
+      if (c == '"') return true;
+      if (c < 0x20) return fail("invalid character in string literal");
+      if (c != '\\') { out += (char)c; continue; }
+      if (i >= t.size()) return fail("unexpected end of JSON input");
+      char e = t[i++];
+      switch (e) {
+        case '"': out += '"'; break;
+        case '\\': out += '\\'; break;
+        case '/': out += '/'; break;
+        case 'b': out += '\b'; break;
+        case 'f': out += '\f'; break;
+        case 'n': out += '\n'; break;
+        case 'r': out += '\r'; break;
+        case 't': out += '\t'; break;
+        case 'u': {
+          uint32_t u;
+          if (!hex4(u)) return false;
+          if (u >= 0xD800 && u < 0xDC00 && i + 6 <= t.size() && t[i] == '\\' && t[i + 1] == 'u') {
+            size_t save = i;
+            i += 2;
+            uint32_t lo;
+            if (!hex4(lo)) return false;
+            if (lo >= 0xDC00 && lo < 0xE000) u = 0x10000 + ((u - 0xD800) << 10) + (lo - 0xDC00);
+            else { i = save; u = 0xFFFD; }
+          } else if (u >= 0xD800 && u < 0xE000) u = 0xFFFD;
+          utf8(out, u);
+          break;
+        }
+        default: return fail("invalid character in string escape code");
+      }
+    }
+  }
+  bool num(JV& v) {
+    size_t b = i;
+    if (i < t.size() && t[i] == '-') i++;
+    if (i >= t.size()) return fail("unexpected end of JSON input");
+    if (t[i] == '0') i++;
+    else if (t[i] >= '1' && t[i] <= '9') { while (i < t.size() && t[i] >= '0' && t[i] <= '9') i++; }
+    else return fail("invalid character in numeric literal");
+    if (i < t.size() && t[i] == '.') {
+      i++;
+      if (i >= t.size() || t[i] < '0' || t[i] > '9') return fail("invalid character after decimal point in numeric literal");
+      while (i < t.size() && t[i] >= '0' && t[i] <= '9') i++;
+    }
+    if (i < t.size() && (t[i] == 'e' || t[i] == 'E')) {
+      i++;
+      if (i < t.size() && (t[i] == '+' || t[i] == '-')) i++;
+      if (i >= t.size() || t[i] < '0' || t[i] > '9') return fail("invalid character in exponent of numeric literal");
+      while (i < t.size() && t[i] >= '0' && t[i] <= '9') i++;
+    }
+    v.kind = JV::Num;
+    v.s = t.substr(b, i - b);
+    return true;
+  }
+  bool value(JV& v) {
+    ws();
+    if (i >= t.size()) return fail("unexpected end of JSON input");
+    if (++depth > 200) return fail("exceeded max depth");
+    bool ok = false;
+    char c = t[i];
+    if (c == '{') {
+      v.kind = JV::Obj;
+      i++;
+      ws();
+      if (i < t.size() && t[i] == '}') { i++; ok = true; }
+      else for (;;) {
+        ws();
+        if (i >= t.size() || t[i] != '"') { fail("invalid character looking for beginning of object key string"); break; }
+        std::string k;
+        if (!str(k)) break;
+        ws();
+        if (i >= t.size() || t[i] != ':') { fail("invalid character after object key"); break; }
+        i++;
+        JV m;
+        if (!value(m)) break;
+        v.o.emplace_back(std::move(k), std::move(m));
+        ws();
+        if (i < t.size() && t[i] == ',') { i++; continue; }
+        if (i < t.size() && t[i] == '}') { i++; ok = true; break; }
+        fail("invalid character after object key:value pair");
+        break;
+      }
+    } else if (c == '[') {
+      v.kind = JV::Arr;
+      i++;
+      ws();
+      if (i < t.size() && t[i] == ']') { i++; ok = true; }
+      else for (;;) {
+        JV m;
+        if (!value(m)) break;
+        v.a.push_back(std::move(m));
+        ws();
+        if (i < t.size() && t[i] == ',') { i++; continue; }
+        if (i < t.size() && t[i] == ']') { i++; ok = true; break; }
+        fail("invalid character after array element");
+        break;
+      }
+    } else if (c == '"') { v.kind = JV::Str; ok = str(v.s); }
+    else if (c == 't') { v.kind = JV::Bool; v.b = true; ok = lit("true"); }
+    else if (c == 'f') { v.kind = JV::Bool; v.b = false; ok = lit("false"); }
+    else if (c == 'n') { v.kind = JV::Null; ok = lit("null"); }
+    else if (c == '-' || (c >= '0' && c <= '9')) ok = num(v);
+    else fail("invalid character looking for beginning of value");
+    depth--;
+    return ok;
+  }
+  bool document(JV& v) {
+    if (!value(v)) return false;
+    ws();
+    if (i != t.size()) return fail("invalid character after top-level value");
+    return true;
+  }
+};
+
+// encoding/json matches object keys to struct fields exactly first, then case-insensitively
+bool key_is(const std::string& k, const char* name) {
+  size_t n = strlen(name);
+  if (k.size() != n) return false;
+  for (size_t i = 0; i < n; i++) {
+    char a = k[i], b = name[i];
+    if (a >= 'A' && a <= 'Z') a = (char)(a - 'A' + 'a');
+    if (b >= 'A' && b <= 'Z') b = (char)(b - 'A' + 'a');
+    if (a != b) return false;
+  }
+  return true;
+}
+const char* kind_name(const JV& v) {
+  switch (v.kind) {
+    case JV::Null: return "null"; case JV::Bool: return "bool"; case JV::Num: return "number";
+    case JV::Str: return "string"; case JV::Arr: return "array"; default: return "object";
+  }
+}
+// a JSON number into a Go integer field: the literal must be a plain integer that fits (else UnmarshalTypeError)
+bool num_to_int(const JV& v, int bits, bool is_unsigned, int64_t& out) {
+  if (v.s.find_first_of(".eE") != std::string::npos) return false;
+  if (is_unsigned && !v.s.empty() && v.s[0] == '-') return false;
+  std::string e;
+  return parse_int(v.s, is_unsigned ? 64 : bits, "ParseInt", out, e);
+}
+std::string type_err(const JV& v, const char* field, const char* gotype) {
+  return std::string("json: cannot unmarshal ") + kind_name(v) + " into Go struct field DeviceInfo." + field + " of type " + gotype;
+}
+
+}  // namespace
+
+// ---- device.DecodeNodeDevices (devices.go:317-381) -------------------------------------------------------
+bool decode_node_csv(const std::string& s, std::vector<Device>& out, std::string& err) {
+  out.clear();
+  if (s.find(':') == std::string::npos) { err = "node annotation missing device separator"; return false; }
+  for (const std::string& val : split(s, ':')) {
+    if (val.empty()) continue;
+    if (val.find(',') == std::string::npos) { err = "malformed node annotation segment: " + quote(val); return false; }
+    const std::vector<std::string> it = split(val, ',');
+    if (it.size() != 7 && it.size() != 9) {
+      err = "unexpected field count " + std::to_string(it.size()) + " in node annotation";
+      return false;
+    }
+    Device d;
+    int64_t v;
+    std::string e;
+    bool hb;
+    if (!parse_int(it[1], 32, "ParseInt", v, e)) { err = "invalid count field: " + e; return false; }
+    d.count = (int32_t)v;
+    if (!parse_int(it[2], 32, "ParseInt", v, e)) { err = "invalid memory field: " + e; return false; }
+    d.devmem = (int32_t)v;
+    if (!parse_int(it[3], 32, "ParseInt", v, e)) { err = "invalid core field: " + e; return false; }
+    d.devcore = (int32_t)v;
+    if (!parse_bool(it[6], hb, e)) { err = "invalid health field: " + e; return false; }
+    d.health = hb;
+    if (!parse_int(it[5], 64, "Atoi", v, e)) { err = "invalid numa field: " + e; return false; }
+    if (v != (int32_t)v) { err = "numa field does not fit the engine's int32: " + it[5]; return false; }   // Go's int is 64-bit; the HBM record is not
+    d.numa = (int32_t)v;
+    d.mode = "hami-core";
+    if (it.size() == 9) {
+      if (!parse_int(it[7], 64, "Atoi", v, e)) { err = "invalid index field: " + e; return false; }
+      if (v < 0) { err = "index field must not be negative: " + std::to_string(v); return false; }
+      if (v > 255) { err = "index field does not fit the engine's 8-bit device index: " + it[7]; return false; }
+      d.index = (uint32_t)v;
+      d.mode = it[8];
+    }
+    d.id = it[0];
+    d.type = it[4];
+    out.push_back(d);
+  }
+  return true;
+}
+
+// ---- device.UnMarshalNodeDevices (devices.go:445-449): json.Unmarshal into []*DeviceInfo --------------
+bool decode_node_json(const std::string& s, std::vector<Device>& out, std::string& err) {
+  out.clear();
+  JParser p(s);
+  JV doc;
+  if (!p.document(doc)) { err = p.err; return false; }
+  if (doc.kind == JV::Null) return true;
+  if (doc.kind != JV::Arr) { err = std::string("json: cannot unmarshal ") + kind_name(doc) + " into Go value of type []*device.DeviceInfo"; return false; }
+  std::string first_err;   // encoding/json keeps decoding after a type error and reports the first one
+  auto bad = [&](const std::string& m) { if (first_err.empty()) first_err = m; };
+  for (const JV& el : doc.a) {
+    Device d;
+    if (el.kind == JV::Null) { err = "null device entry in node annotation"; return false; }   // a nil *DeviceInfo: the reference would dereference it
+    if (el.kind != JV::Obj) { bad(std::string("json: cannot unmarshal ") + kind_name(el) + " into Go value of type device.DeviceInfo"); out.push_back(d); continue; }
+    for (const auto& kv : el.o) {
+      const std::string& k = kv.first;
+      const JV& v = kv.second;
+      if (v.kind == JV::Null) continue;       // null leaves the field at its zero value
+      int64_t n;
+      if (key_is(k, "id")) { if (v.kind == JV::Str) d.id = v.s; else bad(type_err(v, "id", "string")); }
+      else if (key_is(k, "type")) { if (v.kind == JV::Str) d.type = v.s; else bad(type_err(v, "type", "string")); }
+      else if (key_is(k, "mode")) { if (v.kind == JV::Str) d.mode = v.s; else bad(type_err(v, "mode", "string")); }
+      else if (key_is(k, "devicevendor")) { if (v.kind != JV::Str) bad(type_err(v, "devicevendor", "string")); }
+      else if (key_is(k, "health")) { if (v.kind == JV::Bool) d.health = v.b; else bad(type_err(v, "health", "bool")); }
+      else if (key_is(k, "index")) {
+        if (v.kind == JV::Num && num_to_int(v, 64, true, n)) { if (n > 255) bad("index does not fit the engine's 8-bit device index"); d.index = (uint32_t)n; }
+        else bad(type_err(v, "index", "uint"));
+      }
+      else if (key_is(k, "count")) { if (v.kind == JV::Num && num_to_int(v, 32, false, n)) d.count = (int32_t)n; else bad(type_err(v, "count", "int32")); }
+      else if (key_is(k, "devmem")) { if (v.kind == JV::Num && num_to_int(v, 32, false, n)) d.devmem = (int32_t)n; else bad(type_err(v, "devmem", "int32")); }
+      else if (key_is(k, "devcore")) { if (v.kind == JV::Num && num_to_int(v, 32, false, n)) d.devcore = (int32_t)n; else bad(type_err(v, "devcore", "int32")); }
+      else if (key_is(k, "numa")) {
+        if (v.kind == JV::Num && num_to_int(v, 64, false, n)) { if (n != (int32_t)n) bad("numa does not fit the engine's int32"); d.numa = (int32_t)n; }
+        else bad(type_err(v, "numa", "int"));
+      }
+      else if (key_is(k, "migProfiles")) { if (v.kind == JV::Arr) d.has_mig_profiles = !v.a.empty(); else bad(type_err(v, "migProfiles", "[]device.MigProfile")); }
+      else if (key_is(k, "migtemplate")) { if (v.kind != JV::Arr) bad(type_err(v, "migtemplate", "[]device.Geometry")); }
+      else if (key_is(k, "custominfo")) {
+        if (v.kind != JV::Obj) { bad(type_err(v, "custominfo", "map[string]interface {}")); continue; }
+        // map[string]any: numbers arrive as float64; Ascend reads CustomInfo["NetworkID"] (ascend/device.go:340-352)
+        for (const auto& ci : v.o)
+          if (ci.first == "NetworkID" && ci.second.kind == JV::Num) d.network_id = (int32_t)std::strtod(ci.second.s.c_str(), nullptr);
+      }
+      // unknown keys are ignored
+    }
+    out.push_back(d);
+  }
+  if (!first_err.empty()) { err = first_err; out.clear(); return false; }
+  return true;
+}
+
+// ---- device.DecodePairScores (devices.go:383-389) + the fit loop of GetNodeDevices (nvidia/device.go:319-340)
+// DevicePairScores = []DevicePairScore{ID `json:"uuid"`, Scores map[string]int `json:"score"`}; the FIRST record whose
+// uuid equals a device's ID is attached to it; a device without a record keeps an empty score map (all 0).
+bool decode_pair_scores(const std::string& json, const std::vector<Device>& devs, std::vector<int32_t>& scores, std::string& err) {
+  const size_t n = devs.size();
+  scores.assign(n * n, 0);
+  JParser p(json);
+  JV doc;
+  if (!p.document(doc)) { err = p.err; return false; }
+  if (doc.kind == JV::Null) return true;
+  if (doc.kind != JV::Arr) { err = std::string("json: cannot unmarshal ") + kind_name(doc) + " into Go value of type device.DevicePairScores"; return false; }
+  struct Rec { std::string uuid; std::map<std::string, int64_t> sc; };
+  std::vector<Rec> recs;
+  for (const JV& el : doc.a) {
+    Rec r;
+    if (el.kind == JV::Null) { recs.push_back(r); continue; }
+    if (el.kind != JV::Obj) { err = std::string("json: cannot unmarshal ") + kind_name(el) + " into Go value of type device.DevicePairScore"; return false; }
+    for (const auto& kv : el.o) {
+      if (kv.second.kind == JV::Null) continue;
+      if (key_is(kv.first, "uuid")) {
+        if (kv.second.kind != JV::Str) { err = std::string("json: cannot unmarshal ") + kind_name(kv.second) + " into Go struct field DevicePairScore.uuid of type string"; return false; }
+        r.uuid = kv.second.s;
+      } else if (key_is(kv.first, "score")) {
+        if (kv.second.kind != JV::Obj) { err = std::string("json: cannot unmarshal ") + kind_name(kv.second) + " into Go struct field DevicePairScore.score of type map[string]int"; return false; }
+        for (const auto& m : kv.second.o) {
+          int64_t v = 0;
+          if (m.second.kind == JV::Null) { r.sc[m.first] = 0; continue; }
+          if (m.second.kind != JV::Num || !num_to_int(m.second, 64, false, v)) {
+            err = std::string("json: cannot unmarshal ") + kind_name(m.second) + " into Go struct field DevicePairScore.score of type int";
+            return false;
+          }
+          r.sc[m.first] = v;
+        }
+      }
+    }
+    recs.push_back(r);
+  }
+  for (size_t i = 0; i < n; i++)
+    for (const Rec& r : recs) {
+      if (r.uuid != devs[i].id) continue;
+      for (size_t j = 0; j < n; j++) {
+        auto it = r.sc.find(devs[j].id);
+        if (it != r.sc.end()) scores[i * n + j] = (int32_t)it->second;
+      }
+      break;
+    }
+  return true;
+}
+
+// ---- device.DecodePodDevices / DecodeContainerDevices (devices.go:496-556) -------------------------------
+bool decode_pod_devices(const std::vector<std::pair<std::string, std::string>>& checklist,
+                        const std::vector<std::pair<std::string, std::string>>& annos, std::vector<PodEntry>& out, std::string& err) {
+  out.clear();
+  if (annos.empty()) return true;
+  std::map<std::string, std::string> keys(checklist.begin(), checklist.end());   // the result is a map: key order is not observable, sort it
+  for (const auto& ck : keys) {
+    const std::string* str = nullptr;
+    for (const auto& a : annos) if (a.first == ck.second) str = &a.second;       // a later duplicate annotation wins, like a map
+    if (!str) continue;
+    uint32_t cidx = 0;
+    for (const std::string& seg : split(*str, ';')) {    // every segment is a container, empty ones included (index mapping)
+      size_t before = out.size();
+      if (!seg.empty())
+        for (const std::string& val : split(seg, ':')) {
+          if (val.find(',') == std::string::npos) continue;
+          const std::vector<std::string> f = split(val, ',');
+          if (f.size() < 4) { err = "pod annotation format error, missing fields, do not use nodeName in task spec"; out.clear(); return false; }
+          PodEntry e;
+          e.key = ck.first; e.container = cidx; e.uuid = f[0]; e.type = f[1];
+          int64_t v;
+          std::string pe;
+          if (!parse_int(f[2], 32, "ParseInt", v, pe)) { err = "invalid memory field: " + pe; out.clear(); return false; }
+          e.usedmem = (int32_t)v;
+          if (!parse_int(f[3], 32, "ParseInt", v, pe)) { err = "invalid core field: " + pe; out.clear(); return false; }
+          e.usedcores = (int32_t)v;
+          out.push_back(e);
+        }
+      if (out.size() == before) {
+        PodEntry e;
+        e.key = ck.first; e.container = cidx; e.empty = true;
+        out.push_back(e);
+      }
+      cidx++;
+    }
+  }
+  return true;
+}
+
+// ---- device.CollapseInitContainerUsage / AppContainersOnlyDeviceUsage (initContainer.go:36-157) --------
+void collapse(int mode, uint32_t n_init, const std::vector<PodEntry>& raw, std::vector<PodEntry>& out) {
+  out.clear();
+  struct U { int32_t mem = 0, cores = 0, slots = 0; };
+  std::map<std::string, std::map<std::string, std::pair<U, U>>> acc;   // key → uuid → (init peak, app sum); std::map = sorted by UUID
+  for (const PodEntry& e : raw) {
+    auto& per_key = acc[e.key];                    // a key with only empty containers still yields an (empty) collapsed list
+    if (e.empty) continue;
+    if (e.container < n_init) {
+      if (mode == 1) continue;                     // app-only: init containers are skipped
+      U& u = per_key[e.uuid].first;
+      u.mem = std::max(u.mem, e.usedmem);
+      u.cores = std::max(u.cores, e.usedcores);
+      u.slots = 1;                                 // init containers run one at a time
+    } else {
+      U& u = per_key[e.uuid].second;
+      u.mem += e.usedmem; u.cores += e.usedcores; u.slots++;
+    }
+  }
+  for (const auto& k : acc) {
+    size_t before = out.size();
+    for (const auto& d : k.second) {
+      const U& i = d.second.first;
+      const U& a = d.second.second;
+      PodEntry e;
+      e.key = k.first; e.type = k.first; e.uuid = d.first; e.container = 0;
+      if (mode == 1) { e.usedmem = a.mem; e.usedcores = a.cores; e.slots = a.slots; }
+      else { e.usedmem = std::max(i.mem, a.mem); e.usedcores = std::max(i.cores, a.cores); e.slots = std::max(std::max(i.slots, a.slots), 1); }
+      out.push_back(e);
+    }
+    if (out.size() == before) {
+      PodEntry e;
+      e.key = k.first; e.container = 0; e.empty = true;
+      out.push_back(e);
+    }
+  }
+}
+
+}  // namespace hs_ingest

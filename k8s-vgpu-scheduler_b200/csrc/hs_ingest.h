@@ -1,0 +1,38 @@
+// hs_ingest.h — internal C++ interface of the annotation decoders (see hs_ingest.cc).
+#pragma once
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+namespace hs_ingest {
+
+struct Device {            // device.DeviceInfo, the fields the scheduler path reads (devices.go:127-144)
+  std::string id, type, mode, vendor;
+  uint32_t index = 0;
+  int32_t count = 0, devmem = 0, devcore = 0, numa = 0;
+  bool health = false;
+  int32_t network_id = -1; // CustomInfo["NetworkID"] (Ascend), -1 = absent
+  bool has_mig_profiles = false;
+};
+
+struct PodEntry {          // one ContainerDevice, flattened with its PodDevices key and container index
+  std::string key, uuid, type;
+  uint32_t container = 0;
+  bool empty = false;      // marks an empty ContainerDevices at this (key, container): no device
+  int32_t usedmem = 0, usedcores = 0, slots = 0;
+};
+
+// Each decoder returns true on success; on failure `err` holds the reference's error text.
+bool decode_node_csv(const std::string& s, std::vector<Device>& out, std::string& err);
+bool decode_node_json(const std::string& s, std::vector<Device>& out, std::string& err);
+// scores[i*n+j] = Scores[devs[j].id] of the pair-score record whose uuid is devs[i].id (0 where absent)
+bool decode_pair_scores(const std::string& json, const std::vector<Device>& devs, std::vector<int32_t>& scores, std::string& err);
+// checklist: (PodDevices key, annotation name) pairs; annos: the pod's annotations
+bool decode_pod_devices(const std::vector<std::pair<std::string, std::string>>& checklist,
+                        const std::vector<std::pair<std::string, std::string>>& annos, std::vector<PodEntry>& out, std::string& err);
+// mode 0: CollapseInitContainerUsage, 1: AppContainersOnlyDeviceUsage.  Output: per key (sorted), devices sorted by
+// UUID, container 0; a key whose collapsed list is empty yields one `empty` entry.
+void collapse(int mode, uint32_t n_init, const std::vector<PodEntry>& raw, std::vector<PodEntry>& out);
+
+}  // namespace hs_ingest

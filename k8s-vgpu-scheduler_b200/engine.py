@@ -18,7 +18,8 @@ EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_batch_get", "hs_rollback",
     "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
-    "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
+    "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect",
+    "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
 ]
 
 
@@ -49,6 +50,12 @@ def lib():
     L.hs_shard_init.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64]
     L.hs_rollback.argtypes = [C.c_void_p, C.c_char_p]
     L.hs_snapshot_node.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_device_usage_row), C.c_uint32]
+    L.hs_decode_node_devices.argtypes = [P(abi.hs_vendor_registration), P(P(abi.hs_device_info)), P(C.c_uint32), P(P(C.c_int32))]
+    L.hs_decode_pod_devices.argtypes = [P(abi.hs_kv), C.c_uint32, P(abi.hs_kv), C.c_uint32, P(P(abi.hs_pod_device)), P(C.c_uint32)]
+    L.hs_collapse_pod_devices.argtypes = [C.c_int32, C.c_uint32, P(abi.hs_pod_device), C.c_uint32, P(P(abi.hs_pod_device)), P(C.c_uint32)]
+    L.hs_node_register.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_vendor_registration), C.c_uint32, C.c_char_p, C.c_int8]
+    L.hs_pod_ingest.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, P(abi.hs_kv), C.c_uint32, C.c_uint32]
+    L.hs_pod_shrink.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_kv), C.c_uint32, C.c_uint32]
     L.hs_last_device_ms.restype = C.c_double
     L.hs_last_device_ms.argtypes = [C.c_void_p]
     L.hs_launch_count.restype = C.c_uint64
@@ -64,6 +71,84 @@ def unique_id():
     if rc != 0:
         raise RuntimeError("hs_shard_unique_id failed: %s" % lib().hs_last_error(None).decode())
     return buf.raw
+
+
+class IngestError(Exception):
+    """a decoder refused its input; .rc is the status, str() the reference's error text"""
+
+    def __init__(self, rc, msg):
+        super().__init__(msg)
+        self.rc = rc
+
+
+def _kvs(d):
+    items = list(d.items()) if isinstance(d, dict) else list(d)
+    arr = (abi.hs_kv * max(len(items), 1))()
+    for i, (k, v) in enumerate(items):
+        arr[i].key, arr[i].value = abi._b(k), abi._b(v)
+    return arr, len(items)
+
+
+def _registration(vendor, fmt, annotation, pair_scores=None):
+    return abi.hs_vendor_registration(abi._b(vendor), fmt, abi._b(annotation), abi._b(pair_scores))
+
+
+def decode_node_devices(vendor, fmt, annotation, pair_scores=None):
+    """hs_decode_node_devices (host only, no GPU): (list of DeviceInfo dicts, pair-score matrix or None)."""
+    L = lib()
+    reg = _registration(vendor, fmt, annotation, pair_scores)
+    devs, n, pair = C.POINTER(abi.hs_device_info)(), C.c_uint32(), C.POINTER(C.c_int32)()
+    rc = L.hs_decode_node_devices(C.byref(reg), C.byref(devs), C.byref(n), C.byref(pair))
+    if rc != 0:
+        raise IngestError(rc, L.hs_last_error(None).decode())
+    out = [{"ID": devs[i].id.decode(), "Index": devs[i].index, "Count": devs[i].count, "Devmem": devs[i].devmem,
+            "Devcore": devs[i].devcore, "Type": devs[i].type.decode(), "Numa": devs[i].numa, "Mode": devs[i].mode.decode(),
+            "Health": bool(devs[i].health), "DeviceVendor": devs[i].vendor.decode(), "NetworkID": devs[i].network_id}
+           for i in range(n.value)]
+    return out, ([pair[i] for i in range(n.value * n.value)] if pair else None)
+
+
+def _pod_devices_out(devs, n):
+    out = {}
+    for i in range(n):
+        d = devs[i]
+        ctrs = out.setdefault(d.key.decode(), [])
+        while len(ctrs) <= d.container:
+            ctrs.append([])
+        if d.uuid is not None:
+            ctrs[d.container].append({"UUID": d.uuid.decode(), "Type": d.type.decode(), "Usedmem": d.usedmem,
+                                      "Usedcores": d.usedcores, "Slots": d.slots})
+    return out
+
+
+def decode_pod_devices(checklist, annos):
+    """hs_decode_pod_devices: {key: [[device dict, …] per container]}."""
+    L = lib()
+    ck, nck = _kvs(checklist)
+    an, nan = _kvs(annos)
+    devs, n = C.POINTER(abi.hs_pod_device)(), C.c_uint32()
+    rc = L.hs_decode_pod_devices(ck, nck, an, nan, C.byref(devs), C.byref(n))
+    if rc != 0:
+        raise IngestError(rc, L.hs_last_error(None).decode())
+    return _pod_devices_out(devs, n.value)
+
+
+def collapse_pod_devices(mode, n_init, raw):
+    """hs_collapse_pod_devices; raw in the shape decode_pod_devices returns."""
+    L = lib()
+    flat = []
+    for key, ctrs in raw.items():
+        for c, devs in enumerate(ctrs):
+            if not devs:
+                flat.append(abi.hs_pod_device(abi._b(key), c, None, None, 0, 0, 0))
+            for d in devs or []:
+                flat.append(abi.hs_pod_device(abi._b(key), c, abi._b(d["UUID"]), abi._b(d["Type"]), d["Usedmem"], d["Usedcores"], 0))
+    arr = (abi.hs_pod_device * max(len(flat), 1))(*flat)
+    devs, n = C.POINTER(abi.hs_pod_device)(), C.c_uint32()
+    rc = L.hs_collapse_pod_devices(mode, n_init, arr, len(flat), C.byref(devs), C.byref(n))
+    if rc != 0:
+        raise IngestError(rc, L.hs_last_error(None).decode())
+    return _pod_devices_out(devs, n.value)
 
 
 class PackedOps:
@@ -117,6 +202,9 @@ class Engine:
     def node_upsert(self, node):
         ni, keep = abi.build_node(node)
         return self._check(self.L.hs_node_upsert(self.h, C.byref(ni)))
+
+    def node_count(self):
+        return self.L.hs_node_count(self.h)
 
     def node_remove(self, name):
         return self.L.hs_node_remove(self.h, abi._b(name))
@@ -179,6 +267,19 @@ class Engine:
         blob = C.create_string_buffer(b"".join(handles), 64 * len(handles))
         self.L.hs_shard_connect.argtypes = [C.c_void_p, C.c_void_p, C.c_int32]
         return self._check(self.L.hs_shard_connect(self.h, blob, len(handles)))
+
+    def node_register(self, node, regs, device_cordon=None, hami_vnpu_core=-1):
+        """regs: [(vendor, HS_REG_*, annotation, pair_scores or None)]; returns the number of devices registered."""
+        arr = (abi.hs_vendor_registration * max(len(regs), 1))(*[_registration(*r) for r in regs])
+        return self._check(self.L.hs_node_register(self.h, abi._b(node), arr, len(regs), abi._b(device_cordon), hami_vnpu_core))
+
+    def pod_ingest(self, uid, node, annos, n_init=0):
+        an, n = _kvs(annos)
+        return self.L.hs_pod_ingest(self.h, abi._b(uid), abi._b(node), an, n, n_init)
+
+    def pod_shrink(self, uid, annos, n_init=0):
+        an, n = _kvs(annos)
+        return self.L.hs_pod_shrink(self.h, abi._b(uid), an, n, n_init)
 
     def snapshot(self, node, cap=16):
         rows = (abi.hs_device_usage_row * cap)()

@@ -425,6 +425,12 @@ TABLES = [
     ("check_type", "pkg/device/devices_test.go", "TestCheckType", "tests"),
     ("filter", "pkg/scheduler/scheduler_test.go", "Test_Filter", "tests"),
     ("weights_parse", "pkg/util/device_scoring_weights_test.go", "TestParseDeviceScoringWeights", "tests"),
+    # ingest codecs
+    ("decode_node_devices", "pkg/device/devices_test.go", "Test_DecodeNodeDevices", "tests"),
+    ("unmarshal_node_devices", "pkg/device/devices_test.go", "TestUnMarshalNodeDevices", "tests"),
+    ("decode_pod_devices", "pkg/device/devices_test.go", "Test_DecodePodDevices", "tests"),
+    ("encode_node_devices", "pkg/device/devices_test.go", "Test_EncodeNodeDevices", "tests"),
+    ("marshal_node_devices", "pkg/device/devices_test.go", "TestMarshalNodeDevices", "tests"),
 ]
 
 
