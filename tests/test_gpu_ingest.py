@@ -51,8 +51,9 @@ def registrations(node):
         if vendor == "NVIDIA" and node.get("pair_scores") is not None:
             n = len(node["devices"])
             ids = [x["id"] for x in node["devices"]]
-            pair = json.dumps([{"uuid": ids[i], "score": {ids[j]: int(node["pair_scores"][i * n + j]) for j in range(n) if j != i}}
-                               for i in range(n)])
+            ps = node["pair_scores"]
+            at = (lambda i, j: ps[i][j]) if isinstance(ps[0], (list, tuple)) else (lambda i, j: ps[i * n + j])
+            pair = json.dumps([{"uuid": ids[i], "score": {ids[j]: int(at(i, j)) for j in range(n) if j != i}} for i in range(n)])
         regs.append((vendor, abi.HS_REG_JSON, json.dumps(items), pair))
     return regs
 
