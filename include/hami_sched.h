@@ -353,6 +353,23 @@ int32_t hs_pod_ingest(hs_handle* h, const char* pod_uid, const char* node, const
  * AppContainersOnlyDeviceUsage, once (podManager.UpdatePodDevice).                                           */
 int32_t hs_pod_shrink(hs_handle* h, const char* pod_uid, const hs_kv* annotations, uint32_t n_annotations, uint32_t n_init);
 
+/* ---- simulation: Scheduler.filterSimulation, pkg/scheduler/scheduler.go:1088-1090,1156-1199 -----
+ * hs_filter_dry: Filter against the handle's inventory that releases nothing, commits nothing and remembers
+ * nothing (same result record as hs_filter).
+ * hs_filter_simulate: the cluster-autoscaler path — the candidate nodes arrive WITH the request as node objects;
+ * each is rebuilt from its register annotations with zero usage (buildTransientNodeInfo, :692-711; a node that
+ * yields no device fails with "node unregistered") in a transient inventory on the same GPU, then scored dry.
+ * The result belongs to the handle and is valid until its next call.                                          */
+typedef struct hs_sim_node {
+  const char*                   name;
+  const hs_vendor_registration* regs;
+  uint32_t                      n_regs;
+  const char*                   device_cordon;
+  int8_t                        hami_vnpu_core;
+} hs_sim_node;
+int32_t hs_filter_dry(hs_handle* h, const hs_pod* pod, const char* const* node_names, uint32_t n_names, hs_filter_result* out);
+int32_t hs_filter_simulate(hs_handle* h, const hs_pod* pod, const hs_sim_node* nodes, uint32_t n_nodes, hs_filter_result* out);
+
 /* ---- the allocation-free entry point (it has no counterpart in the reference) --------------------
  * For callers that cannot call cudaMalloc when they need a scan: a plugin whose device memory is a fixed
  * pool carved up at start-up, or a latency-critical path that must not enter the driver's allocator.

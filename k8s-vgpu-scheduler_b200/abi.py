@@ -38,6 +38,11 @@ class hs_pod_device(C.Structure):
                 ("usedmem", C.c_int32), ("usedcores", C.c_int32), ("slots", C.c_int32)]
 
 
+class hs_sim_node(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("regs", C.POINTER(hs_vendor_registration)), ("n_regs", C.c_uint32),
+                ("device_cordon", C.c_char_p), ("hami_vnpu_core", C.c_int8)]
+
+
 HS_REG_CSV, HS_REG_JSON = 0, 1
 
 

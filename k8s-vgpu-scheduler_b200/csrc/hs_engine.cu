@@ -158,6 +158,7 @@ struct OpMeta {           // host-side memory of one op of the current batch
   std::vector<EntryMeta> entries;
   std::vector<uint8_t> ctr_begin;
   int user_op = -1;       // index of the caller's op this device op belongs to
+  bool dry = false;       // filterSimulation: nothing of this op is kept
 };
 
 template <class T>
@@ -248,6 +249,8 @@ struct hs_handle {
   struct FailTab { uint32_t k0, k1, k2; const std::string* s; };
   static constexpr uint32_t kFailTab = 8192;
   std::vector<FailTab> fail_tab = std::vector<FailTab>(kFailTab, FailTab{0, 0, 0, nullptr});
+  hs_handle* sim = nullptr;             // child handle holding the transient inventory of hs_filter_simulate
+  bool dry_run = false;                 // set around hs_filter_dry: ops neither release nor commit
   bool hostprof = false;                // HS_HOSTPROF=1: split the summary time by result kind, printed at hs_destroy
   double prof_s[4] = {0, 0, 0, 0};      // fit / no-fit / other / count
   double host_s[4] = {0, 0, 0, 0};      // diagnostic: cumulative host seconds in compile / device+copies / absorb / summary
@@ -1145,7 +1148,7 @@ void absorb_results(hs_handle* h, int n_ops) {
   for (int op = 0; op < n_ops; op++) {
     const OpMeta& m = h->metas[op];
     const DevDecision& dec = h->b_dec.h[op];
-    if (m.kind == OP_FILTER && m.status == HS_OK && dec.status == 0) {
+    if (m.kind == OP_FILTER && m.status == HS_OK && dec.status == 0 && !m.dry) {
       PodRec pr;
       pr.node = dec.node;
       for (int d = 0; d < HS_D; d++) pr.delta[d] = h->b_delta.h[(size_t)op * HS_D + d];
@@ -1190,13 +1193,14 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
     }
     int rc = compile_pod(h, pod, uuid_pool, c);
     if (rc != HS_OK) { h->user_status[i] = rc; continue; }
-    stage_release(h, uid, in_batch, pods, rel, metas, -1);  // TakeAndDeletePod
+    if (h->dry_run) { c.pod.flags |= PF_DRYRUN; c.meta.dry = true; }   // simulation runs before TakeAndDeletePod (scheduler.go:1088-1094)
+    else stage_release(h, uid, in_batch, pods, rel, metas, -1);  // TakeAndDeletePod
     c.pod.entry_off = (uint32_t)entries.size();
     entries.insert(entries.end(), c.entries.begin(), c.entries.end());
     c.meta.user_op = (int)i;
     pods.push_back(c.pod);
     metas.push_back(c.meta);
-    in_batch[uid] = (int)pods.size() - 1;
+    if (!h->dry_run) in_batch[uid] = (int)pods.size() - 1;
     h->user_first_op[i] = (int)pods.size() - 1;
     alloc_cap += c.max_alloc;
   }
@@ -1283,6 +1287,7 @@ hs_handle* hs_create(const hs_config* cfg) {
 }
 
 void hs_destroy(hs_handle* h) {
+  if (h && h->sim) { hs_destroy(h->sim); h->sim = nullptr; }
   if (h && h->hostprof)
     fprintf(stderr, "[hs hostprof] summary: fit %.3f ms, no-fit %.3f ms, other %.3f ms over %.0f results\n", 1e3 * h->prof_s[0],
             1e3 * h->prof_s[1], 1e3 * h->prof_s[2], h->prof_s[3]);
@@ -1503,6 +1508,14 @@ int32_t hs_filter(hs_handle* h, const hs_pod* pod, const char* const* node_names
   assemble_result(h, h->user_first_op[0], out);
   h->have_cand = false;
   return out->status;
+}
+
+int32_t hs_filter_dry(hs_handle* h, const hs_pod* pod, const char* const* node_names, uint32_t n_names, hs_filter_result* out) {
+  if (!h) return HS_ERR_INVALID;
+  h->dry_run = true;
+  int32_t rc = hs_filter(h, pod, node_names, n_names, out);
+  h->dry_run = false;
+  return rc;
 }
 
 int32_t hs_run_batch(hs_handle* h, const hs_op* ops, uint32_t n_ops) {

@@ -297,6 +297,7 @@ hs_decide_kernel(const KernelArgs ka) {
     }
 
     const bool spread = pod.flags & PF_NODE_SPREAD;
+    const bool dry = pod.flags & PF_DRYRUN;       // filterSimulation (scheduler.go:1156-1199): decide, do not commit
     const bool fast = pod.fast != 0;
     // streaming mode only: in resident mode the full evaluation runs in parallel everywhere, so the winner can
     // commit straight after the barrier (measured: deferring it to the winner lengthens the critical path)
@@ -436,11 +437,13 @@ hs_decide_kernel(const KernelArgs ka) {
             DevAlloc a;
             a.entry = 0; a.dev = (uint8_t)glane; a.usedcores = (int16_t)fe.cores; a.usedmem = fe.memreq;
             if (off + (uint32_t)my_row < ka.alloc_cap) ka.allocs[off + my_row] = a;
-            int4* p = ka.dyn + (size_t)my_node * HS_D + glane;
-            int4 v = *p;
-            v.x += 1; v.y += fe.memreq; v.z += fe.cores;
-            *p = v;
-            if (resident) { D.used += 1; D.mem += fe.memreq; D.cores += fe.cores; }
+            if (!dry) {
+              int4* p = ka.dyn + (size_t)my_node * HS_D + glane;
+              int4 v = *p;
+              v.x += 1; v.y += fe.memreq; v.z += fe.cores;
+              *p = v;
+              if (resident) { D.used += 1; D.mem += fe.memreq; D.cores += fe.cores; }
+            }
           }
           ka.commit_delta[(size_t)r * HS_D + glane] = delta;
           if (glane == 0) {
@@ -449,8 +452,10 @@ hs_decide_kernel(const KernelArgs ka) {
             dec.fail_slot = 0xffffffffu; dec.pad[0] = dec.pad[1] = 0;
             ka.decisions[r] = dec;
           }
-          dirty = true;
-          if (!resident) { __syncwarp(gmask); if (glane == 0) refresh_node_score(ka, my_node); }
+          if (!dry) {
+            dirty = true;
+            if (!resident) { __syncwarp(gmask); if (glane == 0) refresh_node_score(ka, my_node); }
+          }
         }
       } else if (mine) {
         if (glane == 0) {
@@ -458,8 +463,10 @@ hs_decide_kernel(const KernelArgs ka) {
           collapse_rows(ent, la, my_nalloc, delta);
           const uint32_t off = atomicAdd(ka.counters + 0, my_nalloc);
           for (uint32_t i = 0; i < my_nalloc && off + i < ka.alloc_cap; i++) ka.allocs[off + i] = la[i];
-          store_usage(ka, my_node, delta, +1);
-          refresh_node_score(ka, my_node);
+          if (!dry) {
+            store_usage(ka, my_node, delta, +1);
+            refresh_node_score(ka, my_node);
+          }
           for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)r * HS_D + d] = delta[d];
           DevDecision dec;
           dec.status = 0; dec.node = my_node; dec.score = my_score; dec.alloc_off = off; dec.n_alloc = my_nalloc;
@@ -704,8 +711,10 @@ hs_shard_decide_kernel(const KernelArgs ka, int op) {
       for (uint32_t i = 0; i < out.n_alloc && off + i < ka.alloc_cap; i++) ka.allocs[off + i] = la[i];
       int4 delta[HS_D];
       collapse_rows(ent, la, out.n_alloc, delta);
-      store_usage(ka, node, delta, +1);
-      refresh_node_score(ka, node);
+      if (!(s_pod.flags & PF_DRYRUN)) {
+        store_usage(ka, node, delta, +1);
+        refresh_node_score(ka, node);
+      }
       for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)op * HS_D + d] = delta[d];
       dec.status = 0; dec.node = node; dec.score = sc; dec.alloc_off = off; dec.n_alloc = out.n_alloc;
     } else {

@@ -70,6 +70,7 @@ struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 
 #define PF_TOPOLOGY 4u      // PolicyContains(gpuPolicy, "topology-aware")  (NVIDIA)
 #define PF_NUMA_ASSERT 8u   // nvidia.com/numa-bind parses true (assertNuma)
 #define PF_ASCEND_HAMICORE 16u // huawei.com/vnpu-mode == "hami-core"
+#define PF_DRYRUN 32u       // decide and report the devices, leave the inventory untouched (filterSimulation, scheduler.go:1156-1199)
 
 enum { OP_FILTER = 0, OP_RELEASE = 1, OP_NOP = 2 };
 

@@ -19,7 +19,7 @@ EXPORTS = [
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_batch_get", "hs_rollback",
     "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
     "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect",
-    "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
+    "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_filter_dry", "hs_filter_simulate", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
 ]
 
 
@@ -43,6 +43,8 @@ def lib():
     L.hs_usage_apply.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.c_int32]
     L.hs_pod_delete.argtypes = [C.c_void_p, C.c_char_p]
     L.hs_filter.argtypes = [C.c_void_p, P(abi.hs_pod), P(C.c_char_p), C.c_uint32, P(abi.hs_filter_result)]
+    L.hs_filter_dry.argtypes = [C.c_void_p, P(abi.hs_pod), P(C.c_char_p), C.c_uint32, P(abi.hs_filter_result)]
+    L.hs_filter_simulate.argtypes = [C.c_void_p, P(abi.hs_pod), P(abi.hs_sim_node), C.c_uint32, P(abi.hs_filter_result)]
     L.hs_run_batch.argtypes = [C.c_void_p, P(abi.hs_op), C.c_uint32]
     L.hs_batch_get.argtypes = [C.c_void_p, C.c_uint32, P(abi.hs_filter_result)]
     L.hs_batch_summary.argtypes = [C.c_void_p, P(C.c_uint32), P(C.c_uint32), P(C.c_uint64)]
@@ -215,7 +217,25 @@ class Engine:
     def pod_delete(self, uid):
         return self.L.hs_pod_delete(self.h, abi._b(uid))
 
-    def filter(self, pod, node_names=None):
+    def filter_simulate(self, pod, sim_nodes):
+        """sim_nodes: [(name, regs, device_cordon, hami_vnpu_core)] with regs as in node_register."""
+        p, keep = abi.build_pod(pod)
+        arr = (abi.hs_sim_node * max(len(sim_nodes), 1))()
+        hold = []
+        for i, (name, regs, cordon, vnpu) in enumerate(sim_nodes):
+            ra = (abi.hs_vendor_registration * max(len(regs), 1))(*[_registration(*r) for r in regs])
+            hold.append(ra)
+            arr[i].name, arr[i].regs, arr[i].n_regs = abi._b(name), ra, len(regs)
+            arr[i].device_cordon, arr[i].hami_vnpu_core = abi._b(cordon), vnpu
+        res = abi.hs_filter_result()
+        rc = self.L.hs_filter_simulate(self.h, C.byref(p), arr, len(sim_nodes), C.byref(res))
+        out = abi.read_result(res)
+        out["rc"] = rc
+        if rc < 0:
+            out["error"] = self.error()
+        return out
+
+    def filter(self, pod, node_names=None, dry=False):
         p, keep = abi.build_pod(pod)
         res = abi.hs_filter_result()
         if node_names is None:
@@ -223,7 +243,7 @@ class Engine:
         else:
             names = (C.c_char_p * max(1, len(node_names)))(*[abi._b(x) for x in node_names])
             n = len(node_names)
-        rc = self.L.hs_filter(self.h, C.byref(p), names, n, C.byref(res))
+        rc = (self.L.hs_filter_dry if dry else self.L.hs_filter)(self.h, C.byref(p), names, n, C.byref(res))
         out = abi.read_result(res)
         out["rc"] = rc
         if rc < 0:

@@ -1,0 +1,99 @@
+"""Scheduler.filterSimulation (pkg/scheduler/scheduler.go:1088-1090,1156-1199) through the C ABI:
+
+  hs_filter_dry       decides like Filter but leaves the inventory and the pod cache untouched;
+  hs_filter_simulate  the candidate nodes come with the request as register annotations, carry no usage
+                      (buildTransientNodeInfo) and are scored in a transient inventory.
+The oracle side is the same Filter: for the dry call it decides on a copy-equivalent state (decide, then undo), for
+the simulation it is a fresh oracle that holds only the transient nodes.
+"""
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+import oracle_abi as oa  # noqa: E402
+import parity  # noqa: E402
+from oracle_abi import abi  # noqa: E402
+from test_gpu_ingest import registrations  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+def same_decision(ref, got):
+    if ref["status"] != got["status"]:
+        return False
+    if ref["status"] == abi.HS_FIT:
+        return (ref["node"], parity.f32bits(ref["score"]), ref["devices"], ref["annotations"]) == \
+               (got["node"], parity.f32bits(got["score"]), got["devices"], got["annotations"])
+    return ref["failed"] == got["failed"]
+
+
+def test_dry_filter_decides_without_committing():
+    import k8s_vgpu_scheduler_b200.engine as eng
+    import k8s_vgpu_scheduler_b200.gen as gen
+    cfg, nodes, ops = gen.mixed_features(n_nodes=24, n_pods=600)
+    warm, probes = ops[:300], [a for k, a in ops[300:] if k == "filter"][:120]
+    o = oa.Oracle(cfg.get("node_policy"), cfg.get("gpu_policy"))
+    e = eng.Engine(cfg.get("node_policy"), cfg.get("gpu_policy"))
+    for n in nodes:
+        o.node_upsert(n)
+        e.node_upsert(n)
+    for kind, arg in warm:
+        if kind == "filter":
+            o.filter(arg)
+        else:
+            o.pod_delete(arg)
+    e.run_batch(eng.PackedOps(warm))
+    before = {n["name"]: e.snapshot(n["name"]) for n in nodes}
+    fits = 0
+    for pod in probes:
+        pod = dict(pod, uid="dry-" + pod["uid"])
+        ref = o.filter(pod)
+        o.pod_delete(pod["uid"])                                  # undo: the dry call must equal a decision on untouched state
+        got = e.filter(pod, dry=True)
+        assert same_decision(ref, got), pod["uid"]
+        fits += ref["status"] == abi.HS_FIT
+    assert fits > 20
+    assert {n["name"]: e.snapshot(n["name"]) for n in nodes} == before       # nothing was committed
+    assert {n["name"]: o.snapshot(n["name"]) for n in nodes} == before
+    # a dry call on a pod the engine already holds does not release it either (simulation runs before TakeAndDeletePod)
+    held = next(a for k, a in warm if k == "filter")
+    e.filter(held, dry=True)
+    assert {n["name"]: e.snapshot(n["name"]) for n in nodes} == before
+    e.close()
+    o.close()
+
+
+def test_simulation_on_transient_nodes():
+    import k8s_vgpu_scheduler_b200.engine as eng
+    import k8s_vgpu_scheduler_b200.gen as gen
+    cfg, nodes, ops = gen.config3(n_nodes=40, n_pods=200)
+    cfg4, nodes4, ops4 = gen.config4(n_nodes=60, n_pods=200)
+    e = eng.Engine(cfg.get("node_policy"), cfg.get("gpu_policy"))
+    for n in nodes[:20]:                                           # the live inventory: must stay out of the simulation
+        e.node_upsert(n)
+    e.run_batch(eng.PackedOps(ops[:100]))
+    live_before = {n["name"]: e.snapshot(n["name"]) for n in nodes[:20]}
+    pods = [a for k, a in ops if k == "filter"][:40] + [a for k, a in ops4 if k == "filter"][:60]
+    for i, pod in enumerate(pods):
+        # a different handful of template nodes per request, some of them without any device annotation
+        pool = (nodes[20:] if i < 40 else [n for n in nodes4 if not any(d["vendor"] == "MLU" for d in n["devices"])])
+        chosen = [pool[(i * 7 + j * 3) % len(pool)] for j in range(1 + i % 6)]
+        chosen = list({n["name"]: n for n in chosen}.values())
+        sim = [(n["name"], registrations(n), n.get("device_cordon"), n.get("hami_vnpu_core", -1)) for n in chosen]
+        if i % 5 == 0:
+            sim.insert(len(sim) // 2, ("empty-template-%d" % i, [], None, -1))
+        o = oa.Oracle(cfg.get("node_policy"), cfg.get("gpu_policy"))
+        for n in chosen:
+            o.node_upsert(n)
+        ref = o.filter(pod, [s[0] for s in sim])
+        o.close()
+        got = e.filter_simulate(pod, sim)
+        assert same_decision(ref, got), (i, ref, got)
+        if i % 5 == 0 and ref["status"] == abi.HS_NOFIT:
+            assert got["failed"]["empty-template-%d" % i] == "node unregistered"
+    assert {n["name"]: e.snapshot(n["name"]) for n in nodes[:20]} == live_before
+    e.close()
