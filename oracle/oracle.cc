@@ -473,8 +473,26 @@ ContainerDevices ascendBestCombination910C(int reqNum, const ContainerDevices& c
   return result;
 }
 
+// fitQuota, nvidia/device.go:666-692 and cambricon/device.go:351-376: the pod's hypothetical total (containers placed so
+// far + this container's picks + the candidate device), collapsed, against the namespace quota
+bool fitQuota(const QuotaManager& qm, const ResourceNames& names, const Pod& pod, const ContainerDevices& tmpDevs,
+              const PodDevices* allocated, const std::string& word, const std::string& devUUID, int64_t memreq, int64_t coresreq) {
+  PodDevices hypo;
+  if (allocated) hypo = *allocated;
+  ContainerDevices cur = tmpDevs;
+  ContainerDevice cd;
+  cd.UUID = devUUID; cd.Type = word; cd.Usedmem = (int32_t)memreq; cd.Usedcores = (int32_t)coresreq;
+  cur.push_back(cd);
+  hypo[word].push_back(cur);
+  int64_t mem = 0, core = 0;
+  PodDevices collapsed = CollapseInitContainerUsage(pod.NumInitContainers, hypo);
+  for (auto& ctr : collapsed[word]) for (auto& v : ctr) { mem += v.Usedmem; core += v.Usedcores; }
+  return qm.FitQuota(pod.Namespace, mem, names, core);
+}
+
 FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request,
-                      const Pod& pod, const NodeInfo* nodeInfo, const std::string& gpuPolicyDefault) {
+                      const Pod& pod, const NodeInfo* nodeInfo, const std::string& gpuPolicyDefault,
+                      const PodDevices* allocated, const QuotaManager* quota, const ResourceNames& names) {
   ContainerDeviceRequest k = request;
   int32_t originReq = k.Nums;
   int prevnuma = -1;
@@ -559,7 +577,12 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
     if (k.Coresreq > 100) k.Coresreq = 100;
     if (k.Memreq > 0) memreq = k.Memreq;
     if (k.MemPercentagereq != 101 && k.Memreq == 0) memreq = i32mul(dev->Totalmem, k.MemPercentagereq) / 100;
-    // fitQuota (nvidia/device.go:784, cambricon/device.go:439): the namespace has no quota entry → true (quota.go:73-76)
+    // nvidia/device.go:784-788, cambricon/device.go:439-443 (hygon and ascend Fit do not consult the quota)
+    if ((g.vendor == Vendor::NVIDIA || g.vendor == Vendor::MLU) && quota &&
+        !fitQuota(*quota, names, pod, tmpDevs, allocated, g.vendor == Vendor::NVIDIA ? "NVIDIA" : "MLU", dev->ID, memreq, k.Coresreq)) {
+      reason["ResourceQuotaNotFit"]++;
+      continue;
+    }
     if (i32sub(dev->Totalmem, dev->Usedmem) < memreq) { reason["CardInsufficientMemory"]++; continue; }
     int32_t effectiveTotalCore = dev->Totalcore;
     if (isHAMiCore) effectiveTotalCore = 100;  // ascend/device.go:540-543
@@ -628,10 +651,11 @@ class NvidiaGPUDevices : public Devices {
  public:
   std::string CommonWord() const override { return "NVIDIA"; }
   FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
-                const NodeInfo* nodeInfo, const std::string& def) const override {
+                const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
+                const QuotaManager* quota) const override {
     FitGates g{Vendor::NVIDIA, "NVIDIA", "nvidia.com/use-gputype", "nvidia.com/nouse-gputype",
                "nvidia.com/use-gpuuuid", "nvidia.com/nouse-gpuuuid"};
-    return fitTemplate(g, devices, request, pod, nodeInfo, def);
+    return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
   void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
     // nvidia/device.go:505-518
@@ -648,10 +672,11 @@ class DCUDevices : public Devices {
  public:
   std::string CommonWord() const override { return "DCU"; }
   FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
-                const NodeInfo* nodeInfo, const std::string& def) const override {
+                const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
+                const QuotaManager* quota) const override {
     FitGates g{Vendor::DCU, "DCU", "hygon.com/use-dcutype", "hygon.com/nouse-dcutype",
                "hygon.com/use-gpuuuid", "hygon.com/nouse-gpuuuid"};
-    return fitTemplate(g, devices, request, pod, nodeInfo, def);
+    return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
   void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
     // hygon/device.go:241-251
@@ -667,10 +692,12 @@ class DCUDevices : public Devices {
 class CambriconDevices : public Devices {
  public:
   std::string CommonWord() const override { return "MLU"; }
+  ResourceNames GetResourceNames() const override { return {"MLU/mem", "MLU/core", 256}; }   // cambricon/device.go:60 MemoryFactor
   FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
-                const NodeInfo* nodeInfo, const std::string& def) const override {
+                const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
+                const QuotaManager* quota) const override {
     FitGates g{Vendor::MLU, "MLU", "", "", "cambricon.com/use-gpuuuid", "cambricon.com/nouse-gpuuuid"};
-    return fitTemplate(g, devices, request, pod, nodeInfo, def);
+    return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
   void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
     // cambricon/device.go:312-332
@@ -700,10 +727,11 @@ class AscendDevices : public Devices {
   }
   std::string CommonWord() const override { return cfg_.CommonWord; }
   FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
-                const NodeInfo* nodeInfo, const std::string& def) const override {
+                const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
+                const QuotaManager* quota) const override {
     FitGates g{Vendor::ASCEND, cfg_.CommonWord, "", "",
                "hami.io/use-" + cfg_.CommonWord + "-uuid", "hami.io/no-use-" + cfg_.CommonWord + "-uuid", hamiVnpuCore_};
-    return fitTemplate(g, devices, request, pod, nodeInfo, def);
+    return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
   // ascend/device.go:388-424
   float ScoreNode(const PodSingleDevice& podDevices, const std::string&) const override {
@@ -874,8 +902,73 @@ bool Scheduler::DeletePod(const std::string& uid) {
   if (it == pods_.end()) return false;
   auto n = nodeIndex_.find(it->second.NodeID);
   if (n != nodeIndex_.end()) applyUsage(*nodes_[n->second], it->second.Devices, -1);
+  quota.RmUsage(it->second.Namespace, CountPodDevices(it->second.Devices));   // scheduler.go:250-252,1092-1094
   pods_.erase(it);
   return true;
+}
+
+// ---- pkg/device/quota.go ----------------------------------------------------
+bool QuotaManager::FitQuota(const std::string& ns, int64_t memreq, const ResourceNames& names, int64_t coresreq) const {
+  auto dq = Quotas.find(ns);
+  if (dq == Quotas.end()) return true;
+  auto m = dq->second.find(names.Memory);
+  if (m != dq->second.end()) {
+    int64_t limit = m->second.Limit;
+    if (names.MemoryFactor > 1) limit = limit * (int64_t)names.MemoryFactor;
+    if (m->second.LimitSet && m->second.Used + memreq > limit) return false;
+  }
+  auto c = dq->second.find(names.Core);
+  if (c != dq->second.end() && c->second.LimitSet && c->second.Used + coresreq > c->second.Limit) return false;
+  return true;
+}
+void QuotaManager::AddUsage(const std::string& ns, const std::map<std::string, int64_t>& usage) {
+  if (usage.empty()) return;
+  auto& dp = Quotas[ns];
+  for (auto& kv : usage) dp[kv.first].Used += kv.second;
+}
+void QuotaManager::RmUsage(const std::string& ns, const std::map<std::string, int64_t>& usage) {
+  if (usage.empty()) return;
+  auto dp = Quotas.find(ns);
+  if (dp == Quotas.end()) return;
+  for (auto& kv : usage) {
+    auto q = dp->second.find(kv.first);
+    if (q == dp->second.end()) continue;
+    q->second.Used -= kv.second;
+    if (q->second.Used < 0) q->second.Used = 0;
+  }
+}
+void QuotaManager::SetLimit(const std::string& ns, const std::string& name, int64_t limit) {
+  Quota& q = Quotas[ns][name];
+  q.Limit = limit;
+  q.LimitSet = true;
+}
+void QuotaManager::ClearLimit(const std::string& ns, const std::string& name) {
+  auto dq = Quotas.find(ns);
+  if (dq == Quotas.end()) return;
+  auto q = dq->second.find(name);
+  if (q == dq->second.end()) return;
+  q->second.Limit = 0;
+  q->second.LimitSet = false;
+}
+bool FitQuotaForDevice(const Scheduler& s, const Pod& pod, const ContainerDevices& tmpDevs, const PodDevices* allocated,
+                       const std::string& word, const std::string& devUUID, int64_t memreq, int64_t coresreq) {
+  const Devices* v = s.Vendor(word);
+  if (!v) return true;    // FitQuota: unknown device name → true (quota.go:63-66)
+  return fitQuota(s.quota, v->GetResourceNames(), pod, tmpDevs, allocated, word, devUUID, memreq, coresreq);
+}
+std::map<std::string, int64_t> Scheduler::CountPodDevices(const PodDevices& pd) const {
+  std::map<std::string, int64_t> res;
+  for (auto& kv : pd) {
+    const Devices* v = Vendor(kv.first);
+    if (!v) continue;
+    ResourceNames rn = v->GetResourceNames();
+    for (auto& ctr : kv.second)
+      for (auto& d : ctr) {
+        if (!rn.Memory.empty()) res[rn.Memory] += d.Usedmem;
+        if (!rn.Core.empty()) res[rn.Core] += d.Usedcores;
+      }
+  }
+  return res;
 }
 
 // buildNodeUsage (scheduler.go:654-690) + the usage half of getNodesUsage (:757-842)
@@ -917,7 +1010,7 @@ bool Scheduler::FitInDevices(NodeUsage& node, const ContainerDeviceRequests& req
       reason = "NodeInsufficientDevice";
       return false;
     }
-    FitResult fr = devPlugin->Fit(typeDevices, k, pod, node.Info, cfg_.GPUSchedulerPolicy);
+    FitResult fr = devPlugin->Fit(typeDevices, k, pod, node.Info, cfg_.GPUSchedulerPolicy, &devinput, &quota);
     if (!fr.fit) { reason = fr.reason; return false; }
     for (auto& val : fr.devs) {
       DeviceUsage* d = nullptr;
@@ -1107,7 +1200,9 @@ FilterResult Scheduler::Filter(const Pod& pod, const std::vector<std::string>* n
   PodDevices effective = CollapseInitContainerUsage(pod.NumInitContainers, m.Devices);
   PodInfo pi;
   pi.NodeID = m.NodeID;
+  pi.Namespace = pod.Namespace;
   pi.Devices = effective;
+  quota.AddUsage(pod.Namespace, CountPodDevices(effective));   // scheduler.go:1136-1138
   applyUsage(*nodes_[cand[best]], effective, +1);
   pods_[pod.UID] = pi;
   return fr;

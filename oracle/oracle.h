@@ -145,6 +145,20 @@ struct NodeScore {                 // policy/node_policy.go:27-33
   float Score = 0;
 };
 
+// ---- pkg/device/quota.go ------------------------------------------------------
+struct Quota { int64_t Used = 0, Limit = 0; bool LimitSet = false; };   // quota.go:27-37
+struct ResourceNames { std::string Memory, Core; int32_t MemoryFactor = 1; };   // devices.go ResourceNames
+class QuotaManager {               // quota.go:40-43; keyed namespace -> resource name
+ public:
+  std::map<std::string, std::map<std::string, Quota>> Quotas;
+  // FitQuota, quota.go:62-95 (the vendor lookup is done by the caller, which passes its resource names)
+  bool FitQuota(const std::string& ns, int64_t memreq, const ResourceNames& names, int64_t coresreq) const;
+  void AddUsage(const std::string& ns, const std::map<std::string, int64_t>& usage);     // addUsageLocked, quota.go:136-150
+  void RmUsage(const std::string& ns, const std::map<std::string, int64_t>& usage);      // rmUsageLocked, quota.go:169-184
+  void SetLimit(const std::string& ns, const std::string& name, int64_t limit);          // addQuotaLocked, quota.go:243-268
+  void ClearLimit(const std::string& ns, const std::string& name);                       // delQuotaLocked, quota.go:271-289
+};
+
 // ---- vendor seam: pkg/device/devices.go:34-48 --------------------------------
 struct FitResult {
   bool fit = false;
@@ -156,8 +170,11 @@ class Devices {
  public:
   virtual ~Devices() = default;
   virtual std::string CommonWord() const = 0;
+  // `allocated` = the containers of this pod placed so far (devinput of fitInDevices), `quota` = the manager FitQuota reads
   virtual FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request,
-                        const Pod& pod, const NodeInfo* nodeInfo, const std::string& gpuPolicyDefault) const = 0;
+                        const Pod& pod, const NodeInfo* nodeInfo, const std::string& gpuPolicyDefault,
+                        const PodDevices* allocated = nullptr, const QuotaManager* quota = nullptr) const = 0;
+  virtual ResourceNames GetResourceNames() const { return {CommonWord() + "/mem", CommonWord() + "/core", 1}; }
   virtual float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy) const { return 0; }
   virtual void AddResourceUsage(DeviceUsage& n, const ContainerDevice& ctr) const;
   virtual void PatchAnnotations(const Pod& pod, std::map<std::string, std::string>& annos, const PodDevices& pd) const = 0;
@@ -178,7 +195,7 @@ struct Config {
 };
 
 struct PodInfo {                   // pkg/device/pods.go:33-40
-  std::string NodeID;
+  std::string NodeID, Namespace;
   PodDevices Devices;              // collapsed
 };
 
@@ -209,6 +226,8 @@ class Scheduler {
   bool UsageApply(const std::string& uid, const std::string& node, const std::string& uuid,
                   int32_t slots, int32_t mem, int32_t cores);
   bool DeletePod(const std::string& uid);
+  QuotaManager quota;              // s.quotaManager
+  std::map<std::string, int64_t> CountPodDevices(const PodDevices& pd) const;   // countPodDevices, quota.go:97-117
 
   // Scheduler.Filter (scheduler.go:1067-1154). nodeNames == nullptr: all nodes in registration order.
   FilterResult Filter(const Pod& pod, const std::vector<std::string>* nodeNames);
@@ -258,6 +277,9 @@ bool CheckType(const std::map<std::string, std::string>& annos, const std::strin
 bool PolicyContains(const std::string& policy, const std::string& name);                 // util/util.go:290-298
 std::string GetGPUSchedulerPolicyByPod(const std::string& def, const Pod& pod);         // util/util.go:277-285
 bool ParseDeviceScoringWeights(const std::string& v, DeviceScoringWeights& out, std::string& err);  // util/device_scoring_weights.go:43-102
+// fitQuota (nvidia/device.go:666-692, cambricon/device.go:351-376) for the vendor `word` ("NVIDIA" / "MLU")
+bool FitQuotaForDevice(const Scheduler& s, const Pod& pod, const ContainerDevices& tmpDevs, const PodDevices* allocated,
+                       const std::string& word, const std::string& devUUID, int64_t memreq, int64_t coresreq);
 PodDevices CollapseInitContainerUsage(int numInit, const PodDevices& raw);               // device/initContainer.go:36-114
 std::string EncodePodSingleDevice(const PodSingleDevice& pd);                            // devices.go:451-484
 float ComputeDefaultScore(const DeviceUsageList& devices);                               // policy/node_policy.go:106-130

@@ -445,4 +445,71 @@ int32_t oracle_collapse(const hs_alloc_entry* in, uint32_t n_in, uint32_t n_init
   return (int32_t)n;
 }
 
+static std::string quota_name(oracle_handle* o, const char* vendor, int32_t which) {
+  const Devices* v = o->s->Vendor(str(vendor));
+  if (!v) return "";
+  ResourceNames rn = v->GetResourceNames();
+  return which == 0 ? rn.Memory : rn.Core;
+}
+int32_t oracle_quota_set(oracle_handle* o, const char* ns, const char* vendor, int32_t which, int64_t limit) {
+  std::string name = quota_name(o, vendor, which);
+  if (name.empty()) return HS_ERR_INVALID;    /* IsManagedQuota false: not tracked */
+  o->s->quota.SetLimit(str(ns), name, limit);
+  return HS_OK;
+}
+int32_t oracle_quota_del(oracle_handle* o, const char* ns, const char* vendor, int32_t which) {
+  std::string name = quota_name(o, vendor, which);
+  if (name.empty()) return HS_ERR_INVALID;
+  o->s->quota.ClearLimit(str(ns), name);
+  return HS_OK;
+}
+int32_t oracle_quota_get(oracle_handle* o, const char* ns, const char* vendor, int32_t which, int64_t* limit, int64_t* used, int32_t* limit_set) {
+  std::string name = quota_name(o, vendor, which);
+  auto dq = o->s->quota.Quotas.find(str(ns));
+  if (name.empty() || dq == o->s->quota.Quotas.end()) return HS_ERR_NOTFOUND;
+  auto q = dq->second.find(name);
+  if (q == dq->second.end()) return HS_ERR_NOTFOUND;
+  if (limit) *limit = q->second.Limit;
+  if (used) *used = q->second.Used;
+  if (limit_set) *limit_set = q->second.LimitSet ? 1 : 0;
+  return HS_OK;
+}
+int32_t oracle_quota_add_usage(oracle_handle* o, const char* ns, const char* vendor, int32_t which, int64_t delta) {
+  std::string name = quota_name(o, vendor, which);
+  if (name.empty()) return HS_ERR_INVALID;
+  std::map<std::string, int64_t> u{{name, delta < 0 ? -delta : delta}};
+  if (delta < 0) o->s->quota.RmUsage(str(ns), u); else o->s->quota.AddUsage(str(ns), u);
+  return HS_OK;
+}
+int32_t oracle_fit_quota_scalar(oracle_handle* o, const char* ns, const char* vendor, int64_t memreq, int32_t factor, int64_t coresreq) {
+  const Devices* v = o->s->Vendor(str(vendor));
+  if (!v) return 1;                       /* FitQuota: device not present → true (quota.go:63-66) */
+  ResourceNames rn = v->GetResourceNames();
+  rn.MemoryFactor = factor;
+  return o->s->quota.FitQuota(str(ns), memreq, rn, coresreq) ? 1 : 0;
+}
+int32_t oracle_fit_quota(oracle_handle* o, const char* ns, uint32_t n_init, const hs_alloc_entry* tmp, uint32_t n_tmp,
+                         const hs_alloc_entry* allocated, uint32_t n_allocated, int32_t has_allocated, const char* vendor,
+                         const char* dev_uuid, int64_t memreq, int64_t coresreq) {
+  Pod pod;
+  pod.Namespace = str(ns);
+  pod.NumInitContainers = (int)n_init;
+  ContainerDevices t;
+  for (uint32_t i = 0; i < n_tmp; i++) {
+    ContainerDevice cd;
+    cd.UUID = str(tmp[i].uuid); cd.Type = str(tmp[i].type_key); cd.Usedmem = tmp[i].usedmem; cd.Usedcores = tmp[i].usedcores;
+    t.push_back(cd);
+  }
+  PodDevices alloc;
+  for (uint32_t i = 0; i < n_allocated; i++) {
+    PodSingleDevice& psd = alloc[str(allocated[i].type_key)];
+    if (psd.size() <= allocated[i].container) psd.resize(allocated[i].container + 1);
+    if (!allocated[i].uuid) continue;
+    ContainerDevice cd;
+    cd.UUID = str(allocated[i].uuid); cd.Type = str(allocated[i].type_key); cd.Usedmem = allocated[i].usedmem; cd.Usedcores = allocated[i].usedcores;
+    psd[allocated[i].container].push_back(cd);
+  }
+  return FitQuotaForDevice(*o->s, pod, t, has_allocated ? &alloc : nullptr, str(vendor), str(dev_uuid), memreq, coresreq) ? 1 : 0;
+}
+
 }  // extern "C"

@@ -74,6 +74,20 @@ int32_t oracle_gen_reason(const int32_t* counts, int32_t cards, char* buf, size_
 /* CollapseInitContainerUsage (initContainer.go:36-114): entries in, collapsed entries out (idx field = Slots). */
 int32_t oracle_collapse(const hs_alloc_entry* in, uint32_t n_in, uint32_t n_init, hs_alloc_entry* out, uint32_t cap);
 
+/* QuotaManager (pkg/device/quota.go), keyed by namespace and (vendor word, which: 0 memory / 1 cores): the Go shim
+ * maps "limits.<resource name>" to the vendor through GetResourceNames.  set = addQuotaLocked for one key,
+ * del = delQuotaLocked; get returns 0 when the entry exists. */
+int32_t oracle_quota_set(oracle_handle* o, const char* ns, const char* vendor, int32_t which, int64_t limit);
+int32_t oracle_quota_del(oracle_handle* o, const char* ns, const char* vendor, int32_t which);
+int32_t oracle_quota_get(oracle_handle* o, const char* ns, const char* vendor, int32_t which, int64_t* limit, int64_t* used, int32_t* limit_set);
+/* test hooks for the vectors of pkg/device/quota_test.go: poke Used, and FitQuota with an explicit memory factor */
+int32_t oracle_quota_add_usage(oracle_handle* o, const char* ns, const char* vendor, int32_t which, int64_t delta);
+int32_t oracle_fit_quota_scalar(oracle_handle* o, const char* ns, const char* vendor, int64_t memreq, int32_t factor, int64_t coresreq);
+/* fitQuota (nvidia/device.go:666-692): tmp / allocated as flattened entries (type_key = PodDevices key). 1 = fits. */
+int32_t oracle_fit_quota(oracle_handle* o, const char* ns, uint32_t n_init, const hs_alloc_entry* tmp, uint32_t n_tmp,
+                         const hs_alloc_entry* allocated, uint32_t n_allocated, int32_t has_allocated, const char* vendor,
+                         const char* dev_uuid, int64_t memreq, int64_t coresreq);
+
 #ifdef __cplusplus
 }
 #endif

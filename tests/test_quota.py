@@ -1,0 +1,130 @@
+"""Namespace ResourceQuota on the Fit path: device.QuotaManager (pkg/device/quota.go) and the vendors'
+fitQuota (nvidia/device.go:666-692, cambricon/device.go:351-376).
+
+CPU part: the oracle against the reference's vectors — tests/golden/nvidia_fit_quota.json (TestFitQuota of
+nvidia/device_test.go, 11 cases, extracted) and the scalar cases of pkg/device/quota_test.go (TestFitQuota,
+TestFitQuotaExplicitZeroBlocks, TestAddUsageAndRmUsage; transcribed below with their line numbers).
+GPU part (test_gpu_quota.py): the engine against the oracle on streams in quota'd namespaces.
+"""
+import ctypes as C
+import json
+import os
+
+import oracle_abi as oa
+from oracle_abi import abi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MEM, CORE = 0, 1
+
+
+def _lib():
+    L = oa.lib()
+    L.oracle_quota_set.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int64]
+    L.oracle_quota_del.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32]
+    L.oracle_quota_get.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                   C.POINTER(C.c_int32)]
+    L.oracle_quota_add_usage.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int64]
+    L.oracle_fit_quota_scalar.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_int32, C.c_int64]
+    L.oracle_fit_quota.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.POINTER(abi.hs_alloc_entry), C.c_uint32,
+                                   C.POINTER(abi.hs_alloc_entry), C.c_uint32, C.c_int32, C.c_char_p, C.c_char_p, C.c_int64, C.c_int64]
+    return L
+
+
+def quota_get(L, o, ns, vendor, which):
+    lim, used, st = C.c_int64(), C.c_int64(), C.c_int32()
+    rc = L.oracle_quota_get(o.h, ns.encode(), vendor.encode(), which, C.byref(lim), C.byref(used), C.byref(st))
+    return None if rc != 0 else (lim.value, used.value, bool(st.value))
+
+
+def _entries(rows):
+    arr = (abi.hs_alloc_entry * max(len(rows), 1))()
+    for i, (ctr, key, d) in enumerate(rows):
+        arr[i] = abi.hs_alloc_entry(ctr, key.encode(), d["UUID"].encode(), 0, d["Usedmem"], d["Usedcores"])
+    return arr, len(rows)
+
+
+def test_fit_quota_golden_nvidia():
+    L = _lib()
+    doc = json.load(open(os.path.join(ROOT, "tests", "golden", "nvidia_fit_quota.json")))
+    assert len(doc["cases"]) == 11
+    o = oa.Oracle("binpack", "spread")
+    assert L.oracle_quota_set(o.h, b"default", b"NVIDIA", MEM, 2048) == 0      # limits.nvidia.com/gpumem: 2048 (device_test.go:1324-1339)
+    for c in doc["cases"]:
+        n_init = c["pod"]["args"][0]
+        tmp = [(0, "NVIDIA", d) for d in (c["tmpDevs"].get("NVIDIA", []) if isinstance(c["tmpDevs"], dict) else [])]
+        alloc = []
+        if c["allocated"]:
+            for key, ctrs in c["allocated"].items():
+                key = "NVIDIA" if key == "NvidiaGPUDevice" else key
+                for ci, ctr in enumerate(ctrs):
+                    alloc += [(ci, key, d) for d in ctr]
+        ta, nt = _entries(tmp)
+        aa, na = _entries(alloc)
+        got = L.oracle_fit_quota(o.h, c["ns"].encode(), n_init, ta, nt, aa, na, 1 if c["allocated"] is not None else 0, b"NVIDIA",
+                                 c["devUUID"].encode(), c["memreq"], c["coresreq"])
+        assert bool(got) == c["expectedResult"], c["name"]
+    o.close()
+
+
+def test_fit_quota_scalar_cases():
+    """pkg/device/quota_test.go:121-162 (TestFitQuota) and :164-182 (TestFitQuotaExplicitZeroBlocks)."""
+    L = _lib()
+    o = oa.Oracle("binpack", "spread")
+    ns = b"testns"
+    L.oracle_quota_set(o.h, ns, b"NVIDIA", MEM, 2000)
+    L.oracle_quota_set(o.h, ns, b"NVIDIA", CORE, 400)
+    L.oracle_quota_add_usage(o.h, ns, b"NVIDIA", MEM, 1000)
+    L.oracle_quota_add_usage(o.h, ns, b"NVIDIA", CORE, 200)
+    fit = lambda n, mem, factor, core, dev=b"NVIDIA": bool(L.oracle_fit_quota_scalar(o.h, n, dev, mem, factor, core))   # noqa: E731
+    assert fit(ns, 500, 1, 100)
+    assert not fit(ns, 1500, 1, 100)
+    assert not fit(ns, 500, 1, 300)
+    assert fit(ns, 1000, 2, 100)
+    assert not fit(ns, 5000, 2, 100)
+    assert fit(b"otherns", 1500, 1, 100)
+    assert fit(ns, 1000, 1, 100, b"unknown-device")
+    L.oracle_quota_set(o.h, b"team-zero", b"NVIDIA", MEM, 0)                     # an explicit zero blocks
+    assert not fit(b"team-zero", 500, 1, 0)
+    L.oracle_quota_del(o.h, b"team-zero", b"NVIDIA", MEM)                        # DelQuota: limit gone, entry stays (quota.go:271-289)
+    assert fit(b"team-zero", 500, 1, 0)
+    assert quota_get(L, o, "team-zero", "NVIDIA", MEM) == (0, 0, False)
+    o.close()
+
+
+def test_add_and_rm_usage_clamps_at_zero():
+    """pkg/device/quota_test.go:184-231 (TestAddUsageAndRmUsage)."""
+    L = _lib()
+    o = oa.Oracle("binpack", "spread")
+    ns = b"testns"
+    L.oracle_quota_add_usage(o.h, ns, b"NVIDIA", MEM, 1000)
+    L.oracle_quota_add_usage(o.h, ns, b"NVIDIA", CORE, 100)
+    assert quota_get(L, o, "testns", "NVIDIA", MEM) == (0, 1000, False)          # auto-created by usage tracking: no limit set
+    assert quota_get(L, o, "testns", "NVIDIA", CORE) == (0, 100, False)
+    L.oracle_quota_add_usage(o.h, ns, b"NVIDIA", MEM, -1000)
+    L.oracle_quota_add_usage(o.h, ns, b"NVIDIA", CORE, -100)
+    L.oracle_quota_add_usage(o.h, ns, b"NVIDIA", MEM, -1000)                     # a second removal must not go negative
+    assert quota_get(L, o, "testns", "NVIDIA", MEM) == (0, 0, False)
+    assert quota_get(L, o, "testns", "NVIDIA", CORE) == (0, 0, False)
+    o.close()
+
+
+def test_filter_tracks_quota_usage_in_the_oracle():
+    import k8s_vgpu_scheduler_b200.gen as gen
+    L = _lib()
+    cfg, nodes, ops = gen.mixed_features(n_nodes=12, n_pods=120)
+    o = oa.Oracle(cfg["node_policy"], cfg["gpu_policy"])
+    for n in nodes:
+        o.node_upsert(n)
+    L.oracle_quota_set(o.h, b"default", b"NVIDIA", MEM, 400000)
+    fits = nofit_quota = 0
+    for kind, arg in ops:
+        if kind == "filter":
+            r = o.filter(arg)
+            fits += r["status"] == abi.HS_FIT
+            nofit_quota += r["status"] == abi.HS_NOFIT and any("ResourceQuotaNotFit" in v for v in r["failed"].values())
+        else:
+            o.pod_delete(arg)
+        lim, used, st = quota_get(L, o, "default", "NVIDIA", MEM)
+        assert 0 <= used <= 400000 and st
+    assert fits > 5 and nofit_quota > 5
+    o.close()

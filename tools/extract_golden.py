@@ -431,6 +431,8 @@ TABLES = [
     ("decode_pod_devices", "pkg/device/devices_test.go", "Test_DecodePodDevices", "tests"),
     ("encode_node_devices", "pkg/device/devices_test.go", "Test_EncodeNodeDevices", "tests"),
     ("marshal_node_devices", "pkg/device/devices_test.go", "TestMarshalNodeDevices", "tests"),
+    # namespace quota: quota = limits.nvidia.com/gpumem 2048 in namespace "default" (device_test.go:1324-1339)
+    ("nvidia_fit_quota", "pkg/device/nvidia/device_test.go", "TestFitQuota", "tests"),
 ]
 
 
