@@ -347,8 +347,22 @@ int32_t hs_node_register(hs_handle* h, const char* node, const hs_vendor_registr
  * "*-devices-allocated" annotations, CollapseInitContainerUsage, podManager.AddPod (pods.go:57-97: an existing
  * pod's devices are replaced unless its init-container share was already released).  `node` = the value of
  * hami.io/vgpu-node; it must be registered (HS_ERR_NOTFOUND otherwise: ingest nodes first).                  */
-int32_t hs_pod_ingest(hs_handle* h, const char* pod_uid, const char* node, const hs_kv* annotations, uint32_t n_annotations,
-                      uint32_t n_init);
+int32_t hs_pod_ingest(hs_handle* h, const char* pod_uid, const char* ns, const char* node, const hs_kv* annotations,
+                      uint32_t n_annotations, uint32_t n_init);
+
+/* ---- namespace quota: device.QuotaManager, pkg/device/quota.go ------------------------------
+ * The NVIDIA and MLU Fit refuse a device when the pod's collapsed total would push the namespace past a configured
+ * limit (fitQuota, nvidia/device.go:666-692,784-788; cambricon/device.go:351-376,439-443; reason
+ * "ResourceQuotaNotFit").  hs_quota_set / hs_quota_del = AddQuota / DelQuota for ONE managed key of a ResourceQuota
+ * (quota.go:243-289): the caller maps "limits.<resource name>" to the vendor whose GetResourceNames() lists it and to
+ * which = 0 (memory) or 1 (cores).  Used is maintained by every commit, release, hs_pod_ingest / hs_pod_shrink /
+ * hs_pod_delete (AddUsage / RmUsage / ReplaceUsage, quota.go:119-196; a removal clamps at zero) for every namespace,
+ * limit or not.  hs_quota_memory_factor = ResourceNames.MemoryFactor (default 1, MLU 256).  Pods of a namespace with a
+ * limit take the general evaluator and end with a second grid barrier; not available on the sharded path.          */
+int32_t hs_quota_set(hs_handle* h, const char* ns, const char* vendor, int32_t which, int64_t limit);
+int32_t hs_quota_del(hs_handle* h, const char* ns, const char* vendor, int32_t which);
+int32_t hs_quota_get(hs_handle* h, const char* ns, const char* vendor, int32_t which, int64_t* limit, int64_t* used, int32_t* limit_set);
+int32_t hs_quota_memory_factor(hs_handle* h, const char* vendor, int32_t factor);
 /* onUpdatePod once every init container has succeeded (scheduler.go:200-222): usage shrinks to
  * AppContainersOnlyDeviceUsage, once (podManager.UpdatePodDevice).                                           */
 int32_t hs_pod_shrink(hs_handle* h, const char* pod_uid, const hs_kv* annotations, uint32_t n_annotations, uint32_t n_init);

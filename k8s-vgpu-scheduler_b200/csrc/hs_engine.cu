@@ -142,6 +142,7 @@ struct PodRec {           // podManager entry: what to subtract when the pod goe
   int node;
   int4 delta[HS_D];
   bool init_released = false;   // PodInfo.InitContainerResourceReleased (pods.go:40-53)
+  std::string ns;               // pod.Namespace, for quotaManager.RmUsage
 };
 
 struct EntryMeta {
@@ -153,7 +154,7 @@ struct EntryMeta {
 struct OpMeta {           // host-side memory of one op of the current batch
   int kind = OP_NOP;      // OP_FILTER / OP_RELEASE / OP_NOP
   int status = HS_OK;     // compile-time verdict: HS_PASSTHROUGH / HS_ERR_*
-  std::string uid, vnpu_mode;
+  std::string uid, vnpu_mode, ns;
   int n_ctr = 0, n_init = 0;
   std::vector<EntryMeta> entries;
   std::vector<uint8_t> ctr_begin;
@@ -249,6 +250,14 @@ struct hs_handle {
   struct FailTab { uint32_t k0, k1, k2; const std::string* s; };
   static constexpr uint32_t kFailTab = 8192;
   std::vector<FailTab> fail_tab = std::vector<FailTab>(kFailTab, FailTab{0, 0, 0, nullptr});
+  // device.QuotaManager (quota.go): (namespace, vendor id) -> {memory, cores}; Used is tracked for every namespace
+  // (addUsageLocked auto-creates entries), rows with a limit set travel to the device with each batch
+  struct QuotaEnt { int64_t limit[2] = {0, 0}; bool set[2] = {false, false}; int64_t used[2] = {0, 0}; };
+  std::map<std::pair<std::string, int>, QuotaEnt> quota;
+  int32_t mem_factor[16] = {1, 1, 256, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};   // ResourceNames.MemoryFactor; MLU = 256 (cambricon/device.go:60)
+  bool any_quota_limit = false;
+  std::vector<std::pair<std::string, int>> quota_rows;           // rows of the current batch's device table
+  DBuf<long long> b_quota;
   hs_handle* sim = nullptr;             // child handle holding the transient inventory of hs_filter_simulate
   bool dry_run = false;                 // set around hs_filter_dry: ops neither release nor commit
   bool hostprof = false;                // HS_HOSTPROF=1: split the summary time by result kind, printed at hs_destroy
@@ -476,12 +485,52 @@ struct Compiled {
 // Everything Filter derives from the pod before it looks at a node: Resourcereqs' output,
 // the per-pod knobs (score.go:139-146,361-364; util.go:277-285; scheduler.go:641-652) and
 // the selector annotations, flattened to integers.
+// Row of (namespace, vendor) in this batch's device quota table, -1 when Fit has nothing to check there (no entry, or no
+// limit set: FitQuota gates on LimitSet, quota.go:84,91).
+int quota_row(hs_handle* h, const std::string& ns, int vid) {
+  if (!h->any_quota_limit) return -1;
+  auto it = h->quota.find({ns, vid});
+  if (it == h->quota.end() || (!it->second.set[0] && !it->second.set[1])) return -1;
+  for (size_t i = 0; i < h->quota_rows.size(); i++)
+    if (h->quota_rows[i].second == vid && h->quota_rows[i].first == ns) return (int)i;
+  h->quota_rows.push_back({ns, vid});
+  return (int)h->quota_rows.size() - 1;
+}
+void quota_rows_for(hs_handle* h, const std::string& ns, DevPod& p) {
+  p.q_idx[0] = quota_row(h, ns, HV_NVIDIA);
+  p.q_idx[1] = quota_row(h, ns, HV_MLU);
+}
+// countPodDevices + addUsageLocked / rmUsageLocked (quota.go:97-184) on the host mirror, all vendors
+void quota_track(hs_handle* h, const std::string& ns, int node, const int4* delta, int sign) {
+  const NodeSlot& nsl = h->nodes[node];
+  int64_t mem[16] = {0}, core[16] = {0};
+  bool any[16] = {false};
+  for (size_t d = 0; d < nsl.devs.size() && d < (size_t)HS_D; d++) {
+    if (!(delta[d].x | delta[d].y | delta[d].z)) continue;
+    const int v = nsl.devs[d].vendor_id & 15;
+    mem[v] += delta[d].y; core[v] += delta[d].z; any[v] = true;
+  }
+  for (int v = 0; v < 16; v++) {
+    if (!any[v]) continue;
+    if (sign > 0) {
+      hs_handle::QuotaEnt& q = h->quota[{ns, v}];
+      q.used[0] += mem[v]; q.used[1] += core[v];
+    } else {
+      auto it = h->quota.find({ns, v});
+      if (it == h->quota.end()) continue;
+      it->second.used[0] = std::max<int64_t>(0, it->second.used[0] - mem[v]);
+      it->second.used[1] = std::max<int64_t>(0, it->second.used[1] - core[v]);
+    }
+  }
+}
+
 int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_pool, Compiled& c) {
   memset(&c.pod, 0, sizeof c.pod);
   c.entries.clear();
   c.meta = OpMeta();
   c.max_alloc = 0;
   c.meta.uid = pod->uid ? pod->uid : "";
+  c.meta.ns = pod->ns ? pod->ns : "";
   c.meta.n_ctr = (int)pod->n_containers;
   c.meta.n_init = (int)std::min(pod->n_init, pod->n_containers);
   bool any = false;
@@ -598,6 +647,8 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
               !(e.flags & EF_ASCEND910)) ? 1 : 0;
     if (h->no_fast) p.fast = 0;
   }
+  quota_rows_for(h, c.meta.ns, p);
+  if (p.q_idx[0] >= 0 || p.q_idx[1] >= 0) p.fast = 0;   // the quota check lives in the general evaluator (hs_eval.cuh)
   c.meta.kind = OP_FILTER;
   c.meta.status = HS_OK;
   return HS_OK;
@@ -697,6 +748,8 @@ int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_ca
   ka.counters = h->b_counters.d;
   ka.pos_base = (int32_t)h->pos_base;
   ka.timing = h->timing ? h->b_timing.d : nullptr;
+  ka.quota = h->quota_rows.empty() ? nullptr : h->b_quota.d;
+  ka.sync2 = h->b_best.d + n_ops;
   ka.world = h->xgpu_connected ? h->shard_world : 1;
   ka.rank = h->shard_rank;
   for (int p = 0; p < 8; p++) ka.mbox_peer[p] = h->mbox_peer[p];
@@ -713,7 +766,7 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
   if (rc != HS_OK) return rc;
   const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
   if (!h->b_dec.ensure(n_ops) || !h->b_alloc.ensure(std::max<uint32_t>(alloc_cap, 1)) || !h->b_delta.ensure((size_t)n_ops * HS_D) ||
-      !h->b_best.ensure(n_ops) || !h->b_counters.ensure(8) || !h->b_fail.ensure((size_t)h->fail_cap * std::max(n_nodes, HS_TILE))) {
+      !h->b_best.ensure((size_t)n_ops * 2) || !h->b_counters.ensure(8) || !h->b_fail.ensure((size_t)h->fail_cap * std::max(n_nodes, HS_TILE))) {
     h->err = "out of device memory for batch buffers";
     return HS_ERR_CUDA;
   }
@@ -723,8 +776,10 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
   if (n_rel) CUDA_OK(h, cudaMemcpyAsync(h->b_rel.d, h->b_rel.h, n_rel * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
   if (h->have_cand) CUDA_OK(h, cudaMemcpyAsync(h->b_candpos.d, h->b_candpos.h, (size_t)n_nodes * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
   CUDA_OK(h, cudaMemsetAsync(h->b_dec.d, 0xff, (size_t)n_ops * sizeof(DevDecision), h->stream));
-  CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, (size_t)n_ops * sizeof(OpSync), h->stream));
+  CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, (size_t)n_ops * 2 * sizeof(OpSync), h->stream));   // [0,n): arg-best slots, [n,2n): quota barriers
   CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
+  if (!h->quota_rows.empty())
+    CUDA_OK(h, cudaMemcpyAsync(h->b_quota.d, h->b_quota.h, h->quota_rows.size() * 4 * sizeof(long long), cudaMemcpyHostToDevice, h->stream));
 
   int block = h->block;
   int maxb = hs_decide_max_blocks(block, h->device);
@@ -1111,10 +1166,13 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
   DevPod p;
   memset(&p, 0, sizeof p);
   p.op = OP_RELEASE;
+  p.q_idx[0] = p.q_idx[1] = -1;
+  std::string rel_ns;
   auto ib = in_batch.find(uid);
   if (ib != in_batch.end()) {
     p.rel_node = -1;
     p.rel_ref = ib->second;
+    rel_ns = metas[ib->second].ns;
     in_batch.erase(ib);
   } else {
     auto it = h->pods.find(uid);
@@ -1132,10 +1190,13 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
     p.rel_node = it->second.node;
     p.rel_off = (int32_t)rel.size();
     for (int d = 0; d < HS_D; d++) rel.push_back(it->second.delta[d]);
+    rel_ns = it->second.ns;
     h->pods.erase(it);
   }
+  quota_rows_for(h, rel_ns, p);
   OpMeta m;
   m.kind = OP_RELEASE;
+  m.ns = rel_ns;
   m.uid = uid;
   m.user_op = user_op;
   pods.push_back(p);
@@ -1153,14 +1214,21 @@ void absorb_results(hs_handle* h, int n_ops) {
       pr.node = dec.node;
       for (int d = 0; d < HS_D; d++) pr.delta[d] = h->b_delta.h[(size_t)op * HS_D + d];
       apply_host_delta(h, dec.node, pr.delta, +1);
+      pr.ns = m.ns;
+      quota_track(h, m.ns, dec.node, pr.delta, +1);
       h->pods[m.uid] = pr;
     } else if (m.kind == OP_RELEASE) {
       const DevPod& p = h->b_pods.h[op];
       if (p.rel_node >= 0) {
         apply_host_delta(h, p.rel_node, h->b_rel.h + p.rel_off, -1);
+        quota_track(h, m.ns, p.rel_node, h->b_rel.h + p.rel_off, -1);
       } else {
         auto it = h->pods.find(m.uid);
-        if (it != h->pods.end()) { apply_host_delta(h, it->second.node, it->second.delta, -1); h->pods.erase(it); }
+        if (it != h->pods.end()) {
+          apply_host_delta(h, it->second.node, it->second.delta, -1);
+          quota_track(h, it->second.ns, it->second.node, it->second.delta, -1);
+          h->pods.erase(it);
+        }
       }
     }
   }
@@ -1180,6 +1248,7 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
   std::unordered_map<std::string, int> in_batch;
   h->user_first_op.assign(n_ops, -1);
   h->user_status.assign(n_ops, HS_OK);
+  h->quota_rows.clear();
   uint32_t alloc_cap = 0;
   Compiled c;
   for (uint32_t i = 0; i < n_ops; i++) {
@@ -1216,6 +1285,18 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
   if (!entries.empty()) memcpy(h->b_entries.h, entries.data(), entries.size() * sizeof(DevEntry));
   if (!uuid_pool.empty()) memcpy(h->b_uuid.h, uuid_pool.data(), uuid_pool.size() * sizeof(uint32_t));
   if (!rel.empty()) memcpy(h->b_rel.h, rel.data(), rel.size() * sizeof(int4));
+  if (!h->quota_rows.empty()) {
+    if (h->shard_world > 1 || h->force_shard) { h->err = "namespace quotas are not supported on the sharded path"; return HS_ERR_UNSUPPORTED; }
+    if (!h->b_quota.ensure(h->quota_rows.size() * 4)) { h->err = "out of memory for the quota table"; return HS_ERR_CUDA; }
+    for (size_t i = 0; i < h->quota_rows.size(); i++) {
+      const hs_handle::QuotaEnt& q = h->quota[h->quota_rows[i]];
+      const int32_t f = h->mem_factor[h->quota_rows[i].second & 15];
+      h->b_quota.h[i * 4 + 0] = q.set[0] ? (f > 1 ? q.limit[0] * (int64_t)f : q.limit[0]) : INT64_MAX;   // quota.go:80-84
+      h->b_quota.h[i * 4 + 1] = q.used[0];
+      h->b_quota.h[i * 4 + 2] = q.set[1] ? q.limit[1] : INT64_MAX;
+      h->b_quota.h[i * 4 + 3] = q.used[1];
+    }
+  }
   const double t1 = now_s();
   const bool launch_per_op = h->force_shard || (h->shard_world > 1 && (!h->xgpu_connected || h->shard_use_nccl));
   int rc = launch_per_op ? run_device_ops_sharded(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap)
@@ -1405,6 +1486,7 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
   bool vnpu = h->ascend_vnpu_default;
   if (ns.vnpu >= 0) vnpu = ns.vnpu == 1;
   if (vnpu) nf |= NF_VNPU_CORE;
+  for (const auto& d : ns.devs) { if (d.type == "NVIDIA") nf |= NF_BASE_NV; if (d.type == "MLU") nf |= NF_BASE_MLU; }
   h->h_flags[slot] = nf;
   {
     h->h_tot[slot] = make_int4((int)nf, host_node_score_bits(h, slot), 0, 0);
@@ -1469,6 +1551,7 @@ int32_t hs_pod_delete(hs_handle* h, const char* pod_uid) {
   auto it = h->pods.find(pod_uid);
   if (it == h->pods.end()) return HS_ERR_NOTFOUND;
   apply_host_delta(h, it->second.node, it->second.delta, -1);
+  quota_track(h, it->second.ns, it->second.node, it->second.delta, -1);
   mark_dirty(h, it->second.node);
   h->pods.erase(it);
   return HS_OK;
@@ -1508,6 +1591,51 @@ int32_t hs_filter(hs_handle* h, const hs_pod* pod, const char* const* node_names
   assemble_result(h, h->user_first_op[0], out);
   h->have_cand = false;
   return out->status;
+}
+
+// QuotaManager.AddQuota / DelQuota for ONE managed key (quota.go:243-289); the caller maps "limits.<resource name>" to
+// the vendor whose GetResourceNames() lists it (IsManagedQuota, quota.go:199-211) and to memory (0) or cores (1).
+static int quota_vendor(hs_handle* h, const char* vendor) {
+  if (!vendor) return -1;
+  for (const auto& v : h->vendors) if (v.word == vendor) return v.id;
+  return -1;
+}
+int32_t hs_quota_set(hs_handle* h, const char* ns, const char* vendor, int32_t which, int64_t limit) {
+  if (!h || !ns || (which != 0 && which != 1)) return HS_ERR_INVALID;
+  const int vid = quota_vendor(h, vendor);
+  if (vid < 0) { h->err = "hs_quota_set: unknown vendor (not a managed quota)"; return HS_ERR_NOTFOUND; }
+  hs_handle::QuotaEnt& q = h->quota[{ns, vid}];
+  q.limit[which] = limit;
+  q.set[which] = true;
+  h->any_quota_limit = true;
+  return HS_OK;
+}
+int32_t hs_quota_del(hs_handle* h, const char* ns, const char* vendor, int32_t which) {
+  if (!h || !ns || (which != 0 && which != 1)) return HS_ERR_INVALID;
+  const int vid = quota_vendor(h, vendor);
+  if (vid < 0) return HS_ERR_NOTFOUND;
+  auto it = h->quota.find({ns, vid});
+  if (it == h->quota.end()) return HS_OK;
+  it->second.limit[which] = 0;          // the entry and its Used stay (quota.go:281-285)
+  it->second.set[which] = false;
+  return HS_OK;
+}
+int32_t hs_quota_get(hs_handle* h, const char* ns, const char* vendor, int32_t which, int64_t* limit, int64_t* used, int32_t* limit_set) {
+  if (!h || !ns || (which != 0 && which != 1)) return HS_ERR_INVALID;
+  const int vid = quota_vendor(h, vendor);
+  auto it = vid < 0 ? h->quota.end() : h->quota.find({ns, vid});
+  if (it == h->quota.end()) return HS_ERR_NOTFOUND;
+  if (limit) *limit = it->second.limit[which];
+  if (used) *used = it->second.used[which];
+  if (limit_set) *limit_set = it->second.set[which] ? 1 : 0;
+  return HS_OK;
+}
+int32_t hs_quota_memory_factor(hs_handle* h, const char* vendor, int32_t factor) {
+  if (!h) return HS_ERR_INVALID;
+  const int vid = quota_vendor(h, vendor);
+  if (vid < 0 || factor < 1) return HS_ERR_INVALID;
+  h->mem_factor[vid & 15] = factor;
+  return HS_OK;
 }
 
 int32_t hs_filter_dry(hs_handle* h, const hs_pod* pod, const char* const* node_names, uint32_t n_names, hs_filter_result* out) {

@@ -143,6 +143,77 @@ struct FitCtx {
   int cores;            // k.Coresreq after the 100 clamp
 };
 
+// Namespace quota (device/quota.go) as the NVIDIA and MLU Fit see it.  fitQuota (nvidia/device.go:666-692,
+// cambricon/device.go:351-376) collapses `allocated` — the containers of this pod placed so far on this node, as the
+// caller built the list — plus the current container (picks so far + the candidate) with CollapseInitContainerUsage
+// and checks the sum.  A list position below numInit counts as an init container (peak per device), the rest as app
+// containers (sum per device); positions restart at 0 for the app phase because score.Devices starts empty
+// (score.go:323-333), which this restates as is.  Index 0 = key "NVIDIA", 1 = key "MLU".
+struct QuotaAcc {
+  long long lim_mem[2], used_mem[2], lim_core[2], used_core[2];
+  bool on[2];
+  int n_init;
+  int len[2];                                // containers in allocated[key], base-type padding included
+  int ipm[2][HS_D], ipc[2][HS_D];            // per device: init peak memory / cores
+  int apm[2][HS_D], apc[2][HS_D];            // per device: app sum memory / cores
+};
+__device__ __forceinline__ void quota_reset_lists(QuotaAcc& q) {
+  for (int v = 0; v < 2; v++) {
+    q.len[v] = 0;
+    for (int d = 0; d < HS_D; d++) { q.ipm[v][d] = q.ipc[v][d] = q.apm[v][d] = q.apc[v][d] = 0; }
+  }
+}
+__device__ __forceinline__ void quota_load(QuotaAcc& q, const DevPod& pod, const KernelArgs& ka) {
+  q.n_init = pod.n_init;
+  for (int v = 0; v < 2; v++) {
+    q.on[v] = pod.q_idx[v] >= 0;
+    if (q.on[v]) {
+      const long long* r = ka.quota + (size_t)pod.q_idx[v] * 4;
+      // through L2: another CTA's commit changed `used` since this SM last read the row
+      q.lim_mem[v] = __ldcg(r + 0); q.used_mem[v] = __ldcg(r + 1); q.lim_core[v] = __ldcg(r + 2); q.used_core[v] = __ldcg(r + 3);
+    }
+  }
+  quota_reset_lists(q);
+}
+// would the pod's collapsed total stay inside the quota if device d joined the current container's picks?
+__device__ __forceinline__ bool quota_fits(const QuotaAcc& q, int v, const int* tmp_dev, const int* tmp_mem, int ntmp,
+                                           int d, int memreq, int cores) {
+  const bool as_init = q.len[v] < q.n_init;
+  long long mem = 0, core = 0;
+  for (int dd = 0; dd < HS_D; dd++) {
+    int cm = 0, cc = 0;
+    bool cur = dd == d;
+    if (cur) { cm = memreq; cc = cores; }
+    for (int t = 0; t < ntmp; t++)
+      if (tmp_dev[t] == dd) { cm += tmp_mem[t]; cc += cores; cur = true; }
+    int im = q.ipm[v][dd], ic = q.ipc[v][dd], am = q.apm[v][dd], ac = q.apc[v][dd];
+    if (cur) {
+      if (as_init) { im = cm > im ? cm : im; ic = cc > ic ? cc : ic; }
+      else { am += cm; ac += cc; }
+    }
+    mem += im > am ? im : am;
+    core += ic > ac ? ic : ac;
+  }
+  if (q.used_mem[v] + mem > q.lim_mem[v]) return false;
+  if (q.used_core[v] + core > q.lim_core[v]) return false;
+  return true;
+}
+// devinput[k.Type] = append(devinput[k.Type], picks) (score.go:132)
+__device__ __forceinline__ void quota_append(QuotaAcc& q, int v, const int* tmp_dev, const int* tmp_mem, int ntmp, int cores) {
+  const bool as_init = q.len[v] < q.n_init;
+  for (int t = 0; t < ntmp; t++) {
+    const int d = tmp_dev[t];
+    if (as_init) {
+      if (tmp_mem[t] > q.ipm[v][d]) q.ipm[v][d] = tmp_mem[t];
+      if (cores > q.ipc[v][d]) q.ipc[v][d] = cores;
+    } else {
+      q.apm[v][d] += tmp_mem[t];
+      q.apc[v][d] += cores;
+    }
+  }
+  q.len[v]++;
+}
+
 #define REASON(r) do { if (MODE == EV_EXPLAIN) out.reasons[r]++; } while (0)
 
 // <vendor>.Fit: nvidia/device.go:715-876, hygon/device.go:264-369, cambricon/device.go:378-488,
@@ -150,8 +221,10 @@ struct FitCtx {
 // td[0..cnt) = typeDevices (device slots, sorted list order).  Returns fit; the picks are in fc.
 template <int MODE>
 __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e, const int* td, int cnt,
-                        uint32_t node, uint32_t nflags, const KernelArgs& ka, FitCtx& fc, EvalOut& out) {
+                        uint32_t node, uint32_t nflags, const KernelArgs& ka, FitCtx& fc, EvalOut& out, const QuotaAcc* qa) {
   const int vendor = e.vendor;
+  const int qv = vendor == HV_NVIDIA ? 0 : (vendor == HV_MLU ? 1 : -1);
+  const bool quota_on = qa != nullptr && qv >= 0 && qa->on[qv];
   const bool isNv = vendor == HV_NVIDIA;
   const bool isAscend = vendor >= HV_ASCEND0;
   int k_nums = e.nums;
@@ -207,6 +280,8 @@ __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e,
     int memreq = 0;
     if (e.memreq > 0) memreq = e.memreq;
     if (e.mempct != 101 && e.memreq == 0) memreq = (int)((unsigned)w.totmem[d] * (unsigned)e.mempct) / 100;
+    // fitQuota, nvidia/device.go:784-788 and cambricon/device.go:439-443
+    if (quota_on && !quota_fits(*qa, qv, fc.tmp_dev, fc.tmp_mem, fc.ntmp, d, memreq, fc.cores)) { REASON(13); continue; }
     if (w.totmem[d] - w.mem[d] < memreq) { REASON(4); continue; }
     const int etc = isHAMiCore ? 100 : w.totcore[d];
     if (etc - w.cores[d] < fc.cores) { REASON(5); continue; }
@@ -349,7 +424,7 @@ __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e,
 template <int MODE>
 __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry* ent, int eb, int ee,
                                   uint32_t node, uint32_t nflags, const KernelArgs& ka, EvalOut& out,
-                                  float* score_acc, uint32_t* score_zero) {
+                                  float* score_acc, uint32_t* score_zero, QuotaAcc* qa) {
   for (int d = 0; d < w.ndev; d++) w.score[d] = dev_compute_score(w, d, pod, ent, eb, ee);
   for (int ei = eb; ei < ee; ei++) {
     const DevEntry& e = ent[ei];
@@ -374,7 +449,9 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
       return false;
     }
     FitCtx fc;
-    if (!dev_fit<MODE>(w, pod, e, td, cnt, node, nflags, ka, fc, out)) return false;
+    if (!dev_fit<MODE>(w, pod, e, td, cnt, node, nflags, ka, fc, out, qa)) return false;
+    if (qa && (e.vendor == HV_NVIDIA || e.vendor == HV_MLU))
+      quota_append(*qa, e.vendor == HV_NVIDIA ? 0 : 1, fc.tmp_dev, fc.tmp_mem, fc.ntmp, fc.cores);
     // AddResourceUsage per pick (nvidia/device.go:645-664 non-MIG; identical for the other vendors)
     int netcnt_max = 0;
     bool missing_net = false;
@@ -419,25 +496,41 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   for (int s = 0; s < HS_SCORE_SLOTS; s++) score_acc[s] = 0.0f;
   const uint32_t identity = 0x76543210u;
   const float pre = node_default_score(w);  // on the pre-allocation usage (score.go:320-328)
+  QuotaAcc qacc;
+  QuotaAcc* qa = nullptr;
+  if (ka.quota != nullptr && (pod.q_idx[0] >= 0 || pod.q_idx[1] >= 0)) { quota_load(qacc, pod, ka); qa = &qacc; }
+  const bool base_key[2] = {(nflags & NF_BASE_NV) != 0, (nflags & NF_BASE_MLU) != 0};
 
   if (pod.n_init > 0) {
     int bu[HS_D], bm[HS_D], bc[HS_D];
     for (int d = 0; d < w.ndev; d++) { bu[d] = w.used[d]; bm[d] = w.mem[d]; bc[d] = w.cores[d]; }
     for (int c = 0; c < pod.n_init && c < pod.n_ctr; c++) {
       const int eb = pod.ctr_begin[c], ee = pod.ctr_begin[c + 1];
-      if (eb == ee) continue;  // len(req) == 0: padded on the host
+      if (eb == ee) {          // len(req) == 0: every base type gets an empty container (score.go:233-238; the rows are padded on the host)
+        if (qa) for (int v = 0; v < 2; v++) if (base_key[v]) qa->len[v]++;
+        continue;
+      }
       w.order = identity;      // node.DeepCopy(): registration order, fresh usage (score.go:241)
-      if (!dev_fit_container<MODE>(w, pod, ent, eb, ee, node, nflags, ka, out, score_acc, &score_zero)) return false;
+      if (!dev_fit_container<MODE>(w, pod, ent, eb, ee, node, nflags, ka, out, score_acc, &score_zero, qa)) return false;
+      if (qa) for (int v = 0; v < 2; v++) if (base_key[v] && qa->len[v] == c) qa->len[v]++;   // score.go:246-250
       for (int d = 0; d < w.ndev; d++) { w.used[d] = bu[d]; w.mem[d] = bm[d]; w.cores[d] = bc[d]; }
     }
   }
   w.order = identity;
+  if (qa) quota_reset_lists(*qa);     // score.Devices starts empty for the app containers (score.go:321-326)
+  int app_index = 0;
   for (int c = pod.n_init; c < pod.n_ctr; c++) {
     const int eb = pod.ctr_begin[c], ee = pod.ctr_begin[c + 1];
     int sums = 0;
     for (int e = eb; e < ee; e++) sums += ent[e].nums;
-    if (sums == 0) continue;
-    if (!dev_fit_container<MODE>(w, pod, ent, eb, ee, node, nflags, ka, out, score_acc, &score_zero)) return false;
+    if (sums == 0) {
+      if (qa) for (int v = 0; v < 2; v++) if (base_key[v]) qa->len[v]++;                         // score.go:266-271
+      app_index++;
+      continue;
+    }
+    if (!dev_fit_container<MODE>(w, pod, ent, eb, ee, node, nflags, ka, out, score_acc, &score_zero, qa)) return false;
+    if (qa) for (int v = 0; v < 2; v++) if (base_key[v] && qa->len[v] == app_index) qa->len[v]++;  // score.go:278-282
+    app_index++;
   }
   // OverrideScore, policy/node_policy.go:67-95: Σ vendor ScoreNode in sorted type-key order
   float devScore = 0.0f;

@@ -81,6 +81,24 @@ __device__ void collapse_rows(const DevEntry* ent, const DevAlloc* al, uint32_t 
   }
 }
 
+// countPodDevices + addUsageLocked / rmUsageLocked (quota.go:97-117,136-150,169-184) for the rows the Fit path reads:
+// the pod's collapsed {slots, mem, cores} per device, summed per vendor; a removal clamps Used at zero.
+__device__ __forceinline__ void quota_apply(const KernelArgs& ka, const DevPod& pod, int node, const int4* delta, int sign) {
+  long long mem[2] = {0, 0}, core[2] = {0, 0};
+  for (int d = 0; d < HS_D; d++) {
+    const uint32_t vendor = PK_VENDOR((uint32_t)ka.stat[(size_t)node * HS_D + d].w);
+    const int qv = vendor == HV_NVIDIA ? 0 : (vendor == HV_MLU ? 1 : -1);
+    if (qv >= 0) { mem[qv] += delta[d].y; core[qv] += delta[d].z; }
+  }
+  for (int v = 0; v < 2; v++) {
+    if (pod.q_idx[v] < 0) continue;
+    long long* row = ka.quota + (size_t)pod.q_idx[v] * 4;
+    const long long m = __ldcg(row + 1) + sign * mem[v], c = __ldcg(row + 3) + sign * core[v];
+    __stcg(row + 1, m < 0 ? 0 : m);
+    __stcg(row + 3, c < 0 ? 0 : c);
+  }
+}
+
 __device__ __forceinline__ void store_usage(const KernelArgs& ka, int node, const int4* delta, int sign) {
   int4* dy = ka.dyn + (size_t)node * HS_D;
   for (int d = 0; d < HS_D; d++) {
@@ -286,6 +304,13 @@ hs_decide_kernel(const KernelArgs ka) {
         }
         dirty = true;
         if (!resident) { __syncwarp(gmask); if (glane == 0) refresh_node_score(ka, node); }
+        if (ka.quota != nullptr && (pod.q_idx[0] >= 0 || pod.q_idx[1] >= 0) && glane == 0)
+          quota_apply(ka, pod, node, rows, -1);               // quotaManager.RmUsage, scheduler.go:250-252
+      }
+      if (ka.quota != nullptr && (pod.q_idx[0] >= 0 || pod.q_idx[1] >= 0)) {   // usage of a quota'd namespace changed: publish it
+        __threadfence();
+        slot_argbest(ka, ka.sync2 + r, 0u, 0ull, s_red, &s_win);
+        __threadfence();
       }
       if (gtid == 0) { ka.decisions[r].status = 2; ka.decisions[r].n_alloc = 0; }
       TICK(1);
@@ -298,6 +323,7 @@ hs_decide_kernel(const KernelArgs ka) {
 
     const bool spread = pod.flags & PF_NODE_SPREAD;
     const bool dry = pod.flags & PF_DRYRUN;       // filterSimulation (scheduler.go:1156-1199): decide, do not commit
+    const bool has_quota = ka.quota != nullptr && (pod.q_idx[0] >= 0 || pod.q_idx[1] >= 0);
     const bool fast = pod.fast != 0;
     // streaming mode only: in resident mode the full evaluation runs in parallel everywhere, so the winner can
     // commit straight after the barrier (measured: deferring it to the winner lengthens the critical path)
@@ -466,6 +492,7 @@ hs_decide_kernel(const KernelArgs ka) {
           if (!dry) {
             store_usage(ka, my_node, delta, +1);
             refresh_node_score(ka, my_node);
+            quota_apply(ka, pod, my_node, delta, +1);      // quotaManager.AddUsage, scheduler.go:1136-1138
           }
           for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)r * HS_D + d] = delta[d];
           DevDecision dec;
@@ -475,6 +502,11 @@ hs_decide_kernel(const KernelArgs ka) {
         }
         __syncwarp(gmask);       // lane 0's stores to the slot rows precede the group's reload
         reload = true;
+      }
+      if (has_quota && !dry) {   // the winner changed a namespace's usage: every CTA must see it before the next sweep
+        __threadfence();
+        slot_argbest(ka, ka.sync2 + r, 0u, 0ull, s_red, &s_win);
+        __threadfence();
       }
     } else {
       // ---- no node fits: per-node reasons for FailedNodes (scheduler.go:1109-1114) ------------

@@ -35,6 +35,8 @@
 #define NF_ALIVE 16u
 #define NF_PAIR_UNIFORM 32u
 #define NF_VNPU_CORE 64u
+#define NF_BASE_NV 128u     // some device of the node has Type == "NVIDIA" exactly: the key pads like a base type (score.go:71-79,246-250)
+#define NF_BASE_MLU 256u    // … Type == "MLU"
 
 // vendor predicate ids (device-side switch, one code path, no dispatch layer)
 enum { HV_NVIDIA = 0, HV_DCU = 1, HV_MLU = 2, HV_ASCEND0 = 3, HV_NONE = 15 };
@@ -89,8 +91,9 @@ struct DevPod {             // one op of the stream, 96 B + entries
   int32_t rel_node;         // node slot, or -1 = take node and deltas from decision `rel_ref` of this batch
   int32_t rel_ref;
   int32_t rel_off;          // first of HS_D {slots, mem, cores, 0} int4 rows in the release pool
-  uint32_t pad4[8];
-  DevEntry e0;              // the first (usually only) entry rides inside the op record: one 160 B prefetch per op
+  int32_t q_idx[2];         // namespace quota rows (KernelArgs.quota) the NVIDIA [0] / MLU [1] Fit consults, -1 = none (quota.go:62-95)
+  uint32_t pad4[6];
+  DevEntry e0;             // the first (usually only) entry rides inside the op record: one 160 B prefetch per op
 };
 static_assert(sizeof(DevEntry) == 64, "DevEntry layout");
 static_assert(sizeof(DevPod) == 160, "DevPod layout: 96 B header + 64 B first entry, 16 B chunks for cp.async");
@@ -163,5 +166,9 @@ struct KernelArgs {
   unsigned long long* xresult;        // local: [4] epoch-tagged global winner, polled by every CTA of this GPU
   uint32_t epoch_base;                // barriers executed by earlier launches of this handle (epochs never restart)
   uint32_t* xerror;                   // set to 1 if a peer never arrived (bounded spin)
+  // namespace quotas with a limit set: [row][4] = {memory limit x factor, memory used, core limit, core used}; a limit that
+  // is not set is INT64_MAX.  Ops of such namespaces end with a second grid barrier (sync2) so the update is visible.
+  long long* quota;
+  OpSync* sync2;                // [op]
   unsigned long long* timing;   // diagnostic: 8 phase-clock accumulators written by block 0 (NULL = off)
 };

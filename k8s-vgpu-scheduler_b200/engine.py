@@ -19,7 +19,7 @@ EXPORTS = [
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_batch_get", "hs_rollback",
     "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
     "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect",
-    "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_filter_dry", "hs_filter_simulate", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
+    "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_filter_dry", "hs_filter_simulate", "hs_quota_set", "hs_quota_del", "hs_quota_get", "hs_quota_memory_factor", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck",
 ]
 
 
@@ -56,7 +56,11 @@ def lib():
     L.hs_decode_pod_devices.argtypes = [P(abi.hs_kv), C.c_uint32, P(abi.hs_kv), C.c_uint32, P(P(abi.hs_pod_device)), P(C.c_uint32)]
     L.hs_collapse_pod_devices.argtypes = [C.c_int32, C.c_uint32, P(abi.hs_pod_device), C.c_uint32, P(P(abi.hs_pod_device)), P(C.c_uint32)]
     L.hs_node_register.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_vendor_registration), C.c_uint32, C.c_char_p, C.c_int8]
-    L.hs_pod_ingest.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, P(abi.hs_kv), C.c_uint32, C.c_uint32]
+    L.hs_pod_ingest.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, P(abi.hs_kv), C.c_uint32, C.c_uint32]
+    L.hs_quota_set.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int64]
+    L.hs_quota_del.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32]
+    L.hs_quota_get.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32, P(C.c_int64), P(C.c_int64), P(C.c_int32)]
+    L.hs_quota_memory_factor.argtypes = [C.c_void_p, C.c_char_p, C.c_int32]
     L.hs_pod_shrink.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_kv), C.c_uint32, C.c_uint32]
     L.hs_last_device_ms.restype = C.c_double
     L.hs_last_device_ms.argtypes = [C.c_void_p]
@@ -293,9 +297,20 @@ class Engine:
         arr = (abi.hs_vendor_registration * max(len(regs), 1))(*[_registration(*r) for r in regs])
         return self._check(self.L.hs_node_register(self.h, abi._b(node), arr, len(regs), abi._b(device_cordon), hami_vnpu_core))
 
-    def pod_ingest(self, uid, node, annos, n_init=0):
+    def pod_ingest(self, uid, node, annos, n_init=0, ns="default"):
         an, n = _kvs(annos)
-        return self.L.hs_pod_ingest(self.h, abi._b(uid), abi._b(node), an, n, n_init)
+        return self.L.hs_pod_ingest(self.h, abi._b(uid), abi._b(ns), abi._b(node), an, n, n_init)
+
+    def quota_set(self, ns, vendor, which, limit):
+        return self._check(self.L.hs_quota_set(self.h, abi._b(ns), abi._b(vendor), which, limit))
+
+    def quota_del(self, ns, vendor, which):
+        return self._check(self.L.hs_quota_del(self.h, abi._b(ns), abi._b(vendor), which))
+
+    def quota_get(self, ns, vendor, which):
+        lim, used, st = C.c_int64(), C.c_int64(), C.c_int32()
+        rc = self.L.hs_quota_get(self.h, abi._b(ns), abi._b(vendor), which, C.byref(lim), C.byref(used), C.byref(st))
+        return None if rc != 0 else (lim.value, used.value, bool(st.value))
 
     def pod_shrink(self, uid, annos, n_init=0):
         an, n = _kvs(annos)
