@@ -1724,7 +1724,9 @@ int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* 
   std::vector<uint32_t> uuid_pool;
   Compiled c;
   int rc = compile_pod(h, pod, uuid_pool, c);
+  h->quota_rows.clear();            // measurement / scan hook: namespace quotas are not consulted
   if (rc != HS_OK) return rc;
+  c.pod.q_idx[0] = c.pod.q_idx[1] = -1;
   c.pod.entry_off = 0;
   if (!h->b_pods.ensure(1) || !h->b_entries.ensure(std::max<size_t>(c.entries.size(), 1)) || !h->b_uuid.ensure(std::max<size_t>(uuid_pool.size(), 1)) ||
       !h->b_best.ensure(1) || !h->b_counters.ensure(8)) { h->err = "out of memory"; return HS_ERR_CUDA; }
@@ -1991,7 +1993,9 @@ extern "C" int32_t hs_sweep_static(hs_handle* h, const hs_pod* pod, void* out_de
   Compiled c;
   h->have_cand = false;
   int rc = compile_pod(h, pod, uuid_pool, c);
+  h->quota_rows.clear();            // measurement / scan hook: namespace quotas are not consulted
   if (rc != HS_OK) return rc;
+  c.pod.q_idx[0] = c.pod.q_idx[1] = -1;
   if (!c.pod.fast || c.pod.e0.has_use || c.pod.e0.nouse_cnt) {
     h->err = "hs_sweep_static: only the common request shape (one request entry, no UUID use/no-use list) is supported without allocation";
     return HS_ERR_UNSUPPORTED;
