@@ -203,6 +203,23 @@ typedef struct hs_ascend_config {
 /* cmd/scheduler/main.go:70-71 flags + the vendor registry of
  * pkg/scheduler/config/config.go:107-251.  NVIDIA, DCU and MLU are always
  * registered; Ascend words as listed.                                       */
+/* A vendor whose Fit is one of the two plain shapes; registered next to the built-in ones.
+ *   HS_FIT_TEMPLATE    iluvatar (pkg/device/iluvatar/device.go:267-371): the gate list of hygon's Fit — health, type,
+ *                      uuid, slots, mutex, memory, cores, exclusive, compute units; checkType = key equals the word
+ *                      (:190-195); one registration per configured CommonWord ("BI-V100", "BI-V150", "MR-V100", …)
+ *   HS_FIT_COUNT_ONLY  biren (pkg/device/biren/device.go:190-248): health, type, uuid, slots, mutex only; the pick
+ *                      records Usedmem 0 and Usedcores = Coresreq as requested (no clamp)
+ * PatchAnnotations of both writes EncodePodSingleDevice under the two keys (iluvatar :143-154, biren :167-177).   */
+enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1 };
+typedef struct hs_vendor_config {
+  const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
+  int32_t     fit_kind;          /* HS_FIT_*                                                                  */
+  const char* use_uuid_key;      /* CheckUUID annotations, e.g. "birentech.com/use-gpuuuid"; NULL = none      */
+  const char* nouse_uuid_key;
+  const char* to_allocate_key;   /* InRequestDevices[word]; NULL = "hami.io/<word>-devices-to-allocate"       */
+  const char* allocated_key;     /* SupportDevices[word];   NULL = "hami.io/<word>-devices-allocated"         */
+} hs_vendor_config;
+
 typedef struct hs_config {
   const char*             node_scheduler_policy;  /* NULL = "binpack" */
   const char*             gpu_scheduler_policy;   /* NULL = "spread"  */
@@ -211,6 +228,8 @@ typedef struct hs_config {
   uint8_t                 ascend_hami_vnpu_core;  /* VNPUs.HamiVnpuCore global default */
   int32_t                 cuda_device;            /* ordinal; -1 = current device      */
   uint32_t                reserve_nodes;          /* initial HBM capacity in nodes (grows on demand) */
+  const hs_vendor_config* vendors;                /* further vendors with a plain Fit; at most 15 vendors in total */
+  uint32_t                n_vendors;
 } hs_config;
 
 typedef struct hs_handle hs_handle;

@@ -94,10 +94,29 @@ class hs_ascend_config(C.Structure):
                 ("templates", C.POINTER(hs_ascend_template)), ("n_templates", C.c_uint32)]
 
 
+class hs_vendor_config(C.Structure):
+    _fields_ = [("common_word", C.c_char_p), ("fit_kind", C.c_int32), ("use_uuid_key", C.c_char_p),
+                ("nouse_uuid_key", C.c_char_p), ("to_allocate_key", C.c_char_p), ("allocated_key", C.c_char_p)]
+
+
+HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY = 0, 1
+
+# The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
+# (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
+DEFAULT_VENDORS = [
+    ("BI-V100", HS_FIT_TEMPLATE, None, None, None, None),
+    ("BI-V150", HS_FIT_TEMPLATE, None, None, None, None),
+    ("MR-V100", HS_FIT_TEMPLATE, None, None, None, None),
+    ("MR-V50", HS_FIT_TEMPLATE, None, None, None, None),
+    ("Biren", HS_FIT_COUNT_ONLY, "birentech.com/use-gpuuuid", "birentech.com/nouse-gpuuuid", None, None),
+]
+
+
 class hs_config(C.Structure):
     _fields_ = [("node_scheduler_policy", C.c_char_p), ("gpu_scheduler_policy", C.c_char_p),
                 ("ascend", C.POINTER(hs_ascend_config)), ("n_ascend", C.c_uint32),
-                ("ascend_hami_vnpu_core", C.c_uint8), ("cuda_device", C.c_int32), ("reserve_nodes", C.c_uint32)]
+                ("ascend_hami_vnpu_core", C.c_uint8), ("cuda_device", C.c_int32), ("reserve_nodes", C.c_uint32),
+                ("vendors", C.POINTER(hs_vendor_config)), ("n_vendors", C.c_uint32)]
 
 
 class hs_op(C.Structure):
@@ -123,8 +142,13 @@ DEFAULT_ASCEND = [
 
 
 def build_config(node_policy=None, gpu_policy=None, ascend=None, ascend_hami_vnpu_core=False,
-                 cuda_device=-1, reserve_nodes=0):
+                 cuda_device=-1, reserve_nodes=0, vendors=None):
     keep = []
+    vendors = DEFAULT_VENDORS if vendors is None else vendors
+    varr = (hs_vendor_config * max(1, len(vendors)))()
+    for i, (word, kind, use, nouse, toalloc, alloc) in enumerate(vendors):
+        varr[i] = hs_vendor_config(_b(word), kind, _b(use), _b(nouse), _b(toalloc), _b(alloc))
+    keep.append(varr)
     ascend = DEFAULT_ASCEND if ascend is None else ascend
     arr = (hs_ascend_config * max(1, len(ascend)))()
     for i, (word, alloc, cap, templates) in enumerate(ascend):
@@ -139,7 +163,7 @@ def build_config(node_policy=None, gpu_policy=None, ascend=None, ascend_hami_vnp
         arr[i].templates = t
         arr[i].n_templates = len(templates)
     cfg = hs_config(_b(node_policy), _b(gpu_policy), arr, len(ascend), 1 if ascend_hami_vnpu_core else 0,
-                    cuda_device, reserve_nodes)
+                    cuda_device, reserve_nodes, varr, len(vendors))
     keep.append(arr)
     return cfg, keep
 

@@ -135,6 +135,8 @@ struct VendorInfo {
   std::string use_type, nouse_type, use_uuid, nouse_uuid;
   std::string to_allocate, allocated;   // InRequestDevices / SupportDevices annotation keys
   bool ascend = false, ascend910 = false;
+  int gate = 0;             // device-side gate class (HV_*): plain vendors share hygon's gate list (HV_DCU)
+  bool count_only = false;  // biren's Fit: no memory / core gates (EF_COUNT_ONLY)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
 };
 
@@ -253,7 +255,17 @@ struct hs_handle {
   // device.QuotaManager (quota.go): (namespace, vendor id) -> {memory, cores}; Used is tracked for every namespace
   // (addUsageLocked auto-creates entries), rows with a limit set travel to the device with each batch
   struct QuotaEnt { int64_t limit[2] = {0, 0}; bool set[2] = {false, false}; int64_t used[2] = {0, 0}; };
-  std::map<std::pair<std::string, int>, QuotaEnt> quota;
+  struct NsQuota { QuotaEnt v[16]; uint32_t present = 0; };      // per namespace: one entry per vendor id, `present` = entry exists
+  std::unordered_map<std::string, NsQuota> quota;
+  QuotaEnt* quota_find(const std::string& ns, int vid) {
+    auto it = quota.find(ns);
+    return (it == quota.end() || !((it->second.present >> vid) & 1u)) ? nullptr : &it->second.v[vid];
+  }
+  QuotaEnt& quota_at(const std::string& ns, int vid) {
+    NsQuota& q = quota[ns];
+    q.present |= 1u << vid;
+    return q.v[vid];
+  }
   int32_t mem_factor[16] = {1, 1, 256, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};   // ResourceNames.MemoryFactor; MLU = 256 (cambricon/device.go:60)
   bool any_quota_limit = false;
   std::vector<std::pair<std::string, int>> quota_rows;           // rows of the current batch's device table
@@ -328,6 +340,7 @@ void add_vendor(hs_handle* h, const std::string& word, bool ascend) {
     v.to_allocate = "hami.io/" + word + "-devices-to-allocate"; v.allocated = "hami.io/" + word + "-devices-allocated";
     v.ascend910 = word.compare(0, 9, "Ascend910") == 0;
   }
+  v.gate = v.id;
   h->vendor_by_word[word] = v.id;
   h->vendors.push_back(v);
 }
@@ -489,8 +502,8 @@ struct Compiled {
 // limit set: FitQuota gates on LimitSet, quota.go:84,91).
 int quota_row(hs_handle* h, const std::string& ns, int vid) {
   if (!h->any_quota_limit) return -1;
-  auto it = h->quota.find({ns, vid});
-  if (it == h->quota.end() || (!it->second.set[0] && !it->second.set[1])) return -1;
+  const hs_handle::QuotaEnt* qe = h->quota_find(ns, vid);
+  if (!qe || (!qe->set[0] && !qe->set[1])) return -1;
   for (size_t i = 0; i < h->quota_rows.size(); i++)
     if (h->quota_rows[i].second == vid && h->quota_rows[i].first == ns) return (int)i;
   h->quota_rows.push_back({ns, vid});
@@ -510,16 +523,20 @@ void quota_track(hs_handle* h, const std::string& ns, int node, const int4* delt
     const int v = nsl.devs[d].vendor_id & 15;
     mem[v] += delta[d].y; core[v] += delta[d].z; any[v] = true;
   }
+  hs_handle::NsQuota* nq = nullptr;
   for (int v = 0; v < 16; v++) {
     if (!any[v]) continue;
+    if (!nq) {
+      if (sign > 0) nq = &h->quota[ns];
+      else { auto it = h->quota.find(ns); if (it == h->quota.end()) return; nq = &it->second; }
+    }
+    hs_handle::QuotaEnt& q = nq->v[v];
     if (sign > 0) {
-      hs_handle::QuotaEnt& q = h->quota[{ns, v}];
+      nq->present |= 1u << v;
       q.used[0] += mem[v]; q.used[1] += core[v];
-    } else {
-      auto it = h->quota.find({ns, v});
-      if (it == h->quota.end()) continue;
-      it->second.used[0] = std::max<int64_t>(0, it->second.used[0] - mem[v]);
-      it->second.used[1] = std::max<int64_t>(0, it->second.used[1] - core[v]);
+    } else if ((nq->present >> v) & 1u) {
+      q.used[0] = std::max<int64_t>(0, q.used[0] - mem[v]);
+      q.used[1] = std::max<int64_t>(0, q.used[1] - core[v]);
     }
   }
 }
@@ -604,7 +621,8 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       e.nums = q->nums; e.memreq = q->memreq; e.mempct = q->mempct; e.coresreq = q->coresreq;
       auto vit = h->vendor_by_word.find(ktype);
       const VendorInfo* v = vit == h->vendor_by_word.end() ? nullptr : &h->vendors[vit->second];
-      e.vendor = v ? (uint16_t)v->id : (uint16_t)HV_NONE;
+      e.vendor = v ? (uint16_t)v->gate : (uint16_t)HV_NONE;
+      if (v && v->count_only) e.flags |= EF_COUNT_ONLY;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
       if (v && v->ascend910) e.flags |= EF_ASCEND910;
@@ -645,7 +663,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     const DevEntry& e = c.entries[0];
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
               !(e.flags & EF_ASCEND910)) ? 1 : 0;
-    if (h->no_fast) p.fast = 0;
+    if (h->no_fast || (e.flags & EF_COUNT_ONLY)) p.fast = 0;
   }
   quota_rows_for(h, c.meta.ns, p);
   if (p.q_idx[0] >= 0 || p.q_idx[1] >= 0) p.fast = 0;   // the quota check lives in the general evaluator (hs_eval.cuh)
@@ -1289,7 +1307,7 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
     if (h->shard_world > 1 || h->force_shard) { h->err = "namespace quotas are not supported on the sharded path"; return HS_ERR_UNSUPPORTED; }
     if (!h->b_quota.ensure(h->quota_rows.size() * 4)) { h->err = "out of memory for the quota table"; return HS_ERR_CUDA; }
     for (size_t i = 0; i < h->quota_rows.size(); i++) {
-      const hs_handle::QuotaEnt& q = h->quota[h->quota_rows[i]];
+      const hs_handle::QuotaEnt& q = h->quota_at(h->quota_rows[i].first, h->quota_rows[i].second);
       const int32_t f = h->mem_factor[h->quota_rows[i].second & 15];
       h->b_quota.h[i * 4 + 0] = q.set[0] ? (f > 1 ? q.limit[0] * (int64_t)f : q.limit[0]) : INT64_MAX;   // quota.go:80-84
       h->b_quota.h[i * 4 + 1] = q.used[0];
@@ -1348,6 +1366,20 @@ hs_handle* hs_create(const hs_config* cfg) {
         v.templates.push_back({cfg->ascend[i].templates[t].name ? cfg->ascend[i].templates[t].name : "", cfg->ascend[i].templates[t].memory});
       std::stable_sort(v.templates.begin(), v.templates.end(),
                        [](const std::pair<std::string, int64_t>& a, const std::pair<std::string, int64_t>& b) { return a.second < b.second; });
+    }
+  if (cfg)
+    for (uint32_t i = 0; i < cfg->n_vendors && h->vendors.size() < 15; i++) {
+      const hs_vendor_config& vc = cfg->vendors[i];
+      if (!vc.common_word || h->vendor_by_word.count(vc.common_word)) continue;
+      add_vendor(h, vc.common_word, false);
+      VendorInfo& v = h->vendors.back();
+      v.ascend910 = false;
+      v.gate = HV_DCU;                      // iluvatar's Fit is hygon's gate list (iluvatar/device.go:267-371)
+      v.count_only = vc.fit_kind == HS_FIT_COUNT_ONLY;
+      if (vc.use_uuid_key) v.use_uuid = vc.use_uuid_key;
+      if (vc.nouse_uuid_key) v.nouse_uuid = vc.nouse_uuid_key;
+      if (vc.to_allocate_key) v.to_allocate = vc.to_allocate_key;
+      if (vc.allocated_key) v.allocated = vc.allocated_key;
     }
   h->modes = {"", "hami-core", "mig", "mps"};
   const char* blk = getenv("HS_BLOCK");
@@ -1604,7 +1636,7 @@ int32_t hs_quota_set(hs_handle* h, const char* ns, const char* vendor, int32_t w
   if (!h || !ns || (which != 0 && which != 1)) return HS_ERR_INVALID;
   const int vid = quota_vendor(h, vendor);
   if (vid < 0) { h->err = "hs_quota_set: unknown vendor (not a managed quota)"; return HS_ERR_NOTFOUND; }
-  hs_handle::QuotaEnt& q = h->quota[{ns, vid}];
+  hs_handle::QuotaEnt& q = h->quota_at(ns, vid);
   q.limit[which] = limit;
   q.set[which] = true;
   h->any_quota_limit = true;
@@ -1614,20 +1646,20 @@ int32_t hs_quota_del(hs_handle* h, const char* ns, const char* vendor, int32_t w
   if (!h || !ns || (which != 0 && which != 1)) return HS_ERR_INVALID;
   const int vid = quota_vendor(h, vendor);
   if (vid < 0) return HS_ERR_NOTFOUND;
-  auto it = h->quota.find({ns, vid});
-  if (it == h->quota.end()) return HS_OK;
-  it->second.limit[which] = 0;          // the entry and its Used stay (quota.go:281-285)
-  it->second.set[which] = false;
+  hs_handle::QuotaEnt* q = h->quota_find(ns, vid);
+  if (!q) return HS_OK;
+  q->limit[which] = 0;                  // the entry and its Used stay (quota.go:281-285)
+  q->set[which] = false;
   return HS_OK;
 }
 int32_t hs_quota_get(hs_handle* h, const char* ns, const char* vendor, int32_t which, int64_t* limit, int64_t* used, int32_t* limit_set) {
   if (!h || !ns || (which != 0 && which != 1)) return HS_ERR_INVALID;
   const int vid = quota_vendor(h, vendor);
-  auto it = vid < 0 ? h->quota.end() : h->quota.find({ns, vid});
-  if (it == h->quota.end()) return HS_ERR_NOTFOUND;
-  if (limit) *limit = it->second.limit[which];
-  if (used) *used = it->second.used[which];
-  if (limit_set) *limit_set = it->second.set[which] ? 1 : 0;
+  const hs_handle::QuotaEnt* q = vid < 0 ? nullptr : h->quota_find(ns, vid);
+  if (!q) return HS_ERR_NOTFOUND;
+  if (limit) *limit = q->limit[which];
+  if (used) *used = q->used[which];
+  if (limit_set) *limit_set = q->set[which] ? 1 : 0;
   return HS_OK;
 }
 int32_t hs_quota_memory_factor(hs_handle* h, const char* vendor, int32_t factor) {

@@ -231,7 +231,8 @@ __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e,
   const int origin = e.nums;
   int prevnuma = -1;
   fc.ntmp = 0;
-  fc.cores = e.coresreq > 100 ? 100 : e.coresreq;
+  const bool countOnly = e.flags & EF_COUNT_ONLY;
+  fc.cores = (e.coresreq > 100 && !countOnly) ? 100 : e.coresreq;
   const bool isMutex = pod.flags & PF_MUTEX;
   bool needTopology = isNv && (pod.flags & PF_TOPOLOGY);
   const bool isHAMiCore = isAscend && (pod.flags & PF_ASCEND_HAMICORE);
@@ -277,6 +278,16 @@ __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e,
     if (!((useMask >> d) & 1u) || ((nouseMask >> d) & 1u)) { REASON(1); continue; }
     if (w.count[d] <= w.used[d]) { REASON(2); continue; }
     if (isMutex && w.used[d] > 0) { REASON(9); continue; }
+    if (countOnly) {                      // biren/device.go:226-241: no memory / core gates, the pick carries no memory
+      if (k_nums > 0) {
+        k_nums--;
+        fc.tmp_dev[fc.ntmp] = d;
+        fc.tmp_mem[fc.ntmp] = 0;
+        fc.ntmp++;
+      }
+      if (k_nums == 0) return true;
+      continue;
+    }
     int memreq = 0;
     if (e.memreq > 0) memreq = e.memreq;
     if (e.mempct != 101 && e.memreq == 0) memreq = (int)((unsigned)w.totmem[d] * (unsigned)e.mempct) / 100;

@@ -360,7 +360,9 @@ void Devices::AddResourceUsage(DeviceUsage& n, const ContainerDevice& ctr) const
 
 namespace {
 
-enum class Vendor { NVIDIA, DCU, MLU, ASCEND };
+// PLAIN: iluvatar's Fit (iluvatar/device.go:267-371) = the hygon gate list with checkType "key equals the word";
+// COUNT_ONLY: biren's Fit (biren/device.go:190-248) = the gates up to mutex, Usedmem 0, Usedcores as requested
+enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY };
 
 struct FitGates {
   Vendor vendor;
@@ -558,6 +560,8 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
           break;
         case Vendor::MLU:
         case Vendor::ASCEND:
+        case Vendor::PLAIN:        // iluvatar/device.go:190-195
+        case Vendor::COUNT_ONLY:   // biren/device.go:130-135
           found = true;
           break;
       }
@@ -574,6 +578,16 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
     int32_t memreq = 0;
     if (dev->Count <= dev->Used) { reason["CardTimeSlicingExhausted"]++; continue; }
     if (isMutex && dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+    if (g.vendor == Vendor::COUNT_ONLY) {   // biren/device.go:226-241: no memory / core gates, the pick carries no memory
+      if (k.Nums > 0) {
+        k.Nums--;
+        ContainerDevice cd;
+        cd.Idx = (int)dev->Index; cd.UUID = dev->ID; cd.Type = k.Type; cd.Usedmem = 0; cd.Usedcores = k.Coresreq;
+        tmpDevs.push_back(cd);
+      }
+      if (k.Nums == 0) { FitResult r; r.fit = true; r.devs = tmpDevs; return r; }
+      continue;
+    }
     if (k.Coresreq > 100) k.Coresreq = 100;
     if (k.Memreq > 0) memreq = k.Memreq;
     if (k.MemPercentagereq != 101 && k.Memreq == 0) memreq = i32mul(dev->Totalmem, k.MemPercentagereq) / 100;
@@ -666,6 +680,31 @@ class NvidiaGPUDevices : public Devices {
       annos["hami.io/vgpu-devices-allocated"] = s;
     }
   }
+};
+
+// iluvatar (one instance per CommonWord, iluvatar/device.go:60-83) and biren (biren/device.go:54-66)
+class PlainDevices : public Devices {
+ public:
+  explicit PlainDevices(const Config::PlainVendor& v) : v_(v) {}
+  std::string CommonWord() const override { return v_.CommonWord; }
+  FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
+                const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
+                const QuotaManager* quota) const override {
+    FitGates g{v_.FitKind == 1 ? Vendor::COUNT_ONLY : Vendor::PLAIN, v_.CommonWord, "", "", v_.UseUUID, v_.NoUseUUID};
+    return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
+  }
+  void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
+    // iluvatar/device.go:143-154, biren/device.go:167-177
+    auto it = pd.find(v_.CommonWord);
+    if (it != pd.end() && !it->second.empty()) {
+      std::string s = EncodePodSingleDevice(it->second);
+      annos[v_.ToAllocate] = s;
+      annos[v_.Allocated] = s;
+    }
+  }
+
+ private:
+  Config::PlainVendor v_;
 };
 
 class DCUDevices : public Devices {
@@ -823,6 +862,7 @@ Scheduler::Scheduler(const Config& cfg) : cfg_(cfg) {
   vendors_["DCU"] = std::make_unique<DCUDevices>();
   vendors_["MLU"] = std::make_unique<CambriconDevices>();
   for (auto& a : cfg.Ascend) vendors_[a.CommonWord] = std::make_unique<AscendDevices>(a, cfg.AscendHamiVnpuCore);
+  for (auto& p : cfg.Plain) vendors_[p.CommonWord] = std::make_unique<PlainDevices>(p);
 }
 Scheduler::~Scheduler() = default;
 

@@ -192,6 +192,9 @@ struct Config {
   std::string GPUSchedulerPolicy = "spread";     // cmd/scheduler/main.go:71
   std::vector<AscendConfig> Ascend;
   bool AscendHamiVnpuCore = false;
+  // vendors with a plain Fit (hs_vendor_config): iluvatar's CommonWords, biren
+  struct PlainVendor { std::string CommonWord; int FitKind = 0; std::string UseUUID, NoUseUUID, ToAllocate, Allocated; };
+  std::vector<PlainVendor> Plain;
 };
 
 struct PodInfo {                   // pkg/device/pods.go:33-40

@@ -131,6 +131,18 @@ oracle_handle* oracle_create(const hs_config* cfg) {
       c.Ascend.push_back(ac);
     }
   }
+  if (cfg)
+    for (uint32_t i = 0; i < cfg->n_vendors; i++) {
+      const hs_vendor_config& v = cfg->vendors[i];
+      Config::PlainVendor pv;
+      pv.CommonWord = str(v.common_word);
+      pv.FitKind = v.fit_kind;
+      pv.UseUUID = v.use_uuid_key ? v.use_uuid_key : "hami.io/use-" + pv.CommonWord + "-uuid";            // iluvatar/device.go:71-72
+      pv.NoUseUUID = v.nouse_uuid_key ? v.nouse_uuid_key : "hami.io/no-use-" + pv.CommonWord + "-uuid";
+      pv.ToAllocate = v.to_allocate_key ? v.to_allocate_key : "hami.io/" + pv.CommonWord + "-devices-to-allocate";
+      pv.Allocated = v.allocated_key ? v.allocated_key : "hami.io/" + pv.CommonWord + "-devices-allocated";
+      c.Plain.push_back(pv);
+    }
   auto* o = new oracle_handle();
   o->s = std::make_unique<Scheduler>(c);
   return o;

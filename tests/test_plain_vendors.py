@@ -1,0 +1,127 @@
+"""Vendors with a plain Fit: iluvatar (pkg/device/iluvatar/device.go:267-371 — hygon's gate list,
+one device type per configured CommonWord) and biren (pkg/device/biren/device.go:190-248 — count-only gates).
+
+CPU: the oracle against the reference's own tables (tests/golden/iluvatar_fit.json = Test_Fit,
+tests/golden/biren_fit.json = TestDevices_Fit) and TestFit_MutexRejectsUsedDevice (iluvatar/device_test.go:421-442).
+GPU: a mixed cluster (NVIDIA + iluvatar + biren nodes) through hs_run_batch against the oracle, bit for bit.
+"""
+import json
+import os
+import random
+
+import pytest
+
+import oracle_abi as oa
+import parity
+from oracle_abi import abi
+from test_oracle_golden import run_fit
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def load(name):
+    return json.load(open(os.path.join(ROOT, "tests", "golden", name + ".json")))["cases"]
+
+
+@pytest.fixture(scope="module")
+def orc():
+    o = oa.Oracle("binpack", "spread")
+    yield o
+    o.close()
+
+
+@pytest.mark.parametrize("case", load("iluvatar_fit"), ids=[c["name"] for c in load("iluvatar_fit")])
+def test_iluvatar_fit(orc, case):
+    annos = case["annos"] if isinstance(case["annos"], dict) else {}
+    fit, got, reason = run_fit(orc, "MR-V100", case["devices"], case["request"], annos)
+    assert fit == case["wantOK"]
+    if fit:
+        assert [g[0] for g in got] == case["wantDevIDs"] and len(got) == case["wantLen"]
+    assert reason == case.get("wantReason", "")
+
+
+def test_iluvatar_mutex_rejects_used_device(orc):
+    dev = {"ID": "dev-0", "Index": 0, "Used": 1, "Count": 100, "Totalmem": 128, "Totalcore": 100, "Numa": 0, "Type": "MR-V100", "Health": True}
+    fit, got, reason = run_fit(orc, "MR-V100", [dev], {"Nums": 1, "Type": "MR-V100", "Memreq": 64, "Coresreq": 50},
+                               {"hami.io/gpu-scheduler-policy": "mutex"})
+    assert not fit and reason == "1/1 ExclusiveDeviceAllocateConflict"
+
+
+@pytest.mark.parametrize("case", load("biren_fit"), ids=[c["name"] for c in load("biren_fit")])
+def test_biren_fit(orc, case):
+    annos = case["annos"] if isinstance(case["annos"], dict) else {}
+    fit, got, reason = run_fit(orc, "Biren", case["devices"], case["request"], annos)
+    assert fit == case["wantFit"]
+    if fit:
+        assert [g[0] for g in got] == case["wantDevIDs"] and len(got) == case["wantLen"]
+        assert all(g[2] == 0 for g in got)                     # Usedmem stays 0 (biren/device.go:231-237)
+    assert reason == case["wantReason"]
+
+
+# ---- GPU parity on a generated cluster ---------------------------------------------------------------------
+def _cluster(n_nodes, n_pods, seed=11):
+    rng = random.Random(seed)
+    nodes, kinds = [], []
+    for i in range(n_nodes):
+        kind = ("NVIDIA", "MR-V100", "BI-V150", "Biren")[i % 4]
+        nd = rng.randrange(2, 9)
+        devs = []
+        for d in range(nd):
+            if kind == "NVIDIA":
+                devs.append({"id": "GPU-%03d-%d" % (i, d), "index": d, "count": 10, "devmem": 81920, "devcore": 100,
+                             "type": "NVIDIA A100-SXM4-80GB", "numa": d // 4, "mode": "hami-core", "health": True, "vendor": "NVIDIA"})
+            elif kind == "Biren":
+                devs.append({"id": "BR-%03d-%d" % (i, d), "index": d, "count": rng.choice([1, 1, 2]), "devmem": 0, "devcore": 0,
+                             "type": "Biren", "numa": 0, "mode": "", "health": rng.random() > 0.05, "vendor": "Biren"})
+            else:
+                devs.append({"id": "ILU-%03d-%d" % (i, d), "index": d, "count": 4, "devmem": 32768, "devcore": 100,
+                             "type": kind, "numa": 0, "mode": "", "health": rng.random() > 0.05, "vendor": kind})
+        nodes.append({"name": "pv-%03d" % i, "devices": devs})
+        kinds.append(kind)
+    ops, live = [], []
+    for p in range(n_pods):
+        kind = rng.choice(["NVIDIA", "MR-V100", "BI-V150", "Biren", "Biren", "MR-V50"])   # MR-V50: registered, no node has it
+        annos = {}
+        if rng.random() < 0.3:
+            annos["hami.io/gpu-scheduler-policy"] = rng.choice(["binpack", "spread", "mutex"])
+        if rng.random() < 0.3:
+            annos["hami.io/node-scheduler-policy"] = rng.choice(["binpack", "spread"])
+        if kind == "Biren":
+            req = {"key": kind, "type": kind, "nums": rng.choice([1, 1, 2, 3]), "memreq": rng.choice([0, 512]), "mempct": 0,
+                   "coresreq": rng.choice([0, 20, 150])}
+            if rng.random() < 0.15:
+                n = rng.choice([x for x, k in zip(nodes, kinds) if k == "Biren"])
+                annos[rng.choice(["birentech.com/use-gpuuuid", "birentech.com/nouse-gpuuuid"])] = n["devices"][0]["id"]
+        else:
+            req = {"key": kind, "type": kind, "nums": rng.choice([1, 1, 2, 4]), "memreq": rng.choice([0, 4096, 16384]),
+                   "mempct": rng.choice([101, 101, 50]), "coresreq": rng.choice([0, 30, 100])}
+            if req["memreq"] == 0 and req["mempct"] == 101:
+                req["mempct"] = 100
+            if kind != "NVIDIA" and rng.random() < 0.15:
+                n = rng.choice([x for x, k in zip(nodes, kinds) if k == kind] or nodes)
+                annos["hami.io/%s-%s-uuid" % (rng.choice(["use", "no-use"]), kind)] = n["devices"][0]["id"]
+        uid = "pv-%05d" % p
+        ctrs = [[req]]
+        if rng.random() < 0.15:
+            ctrs.append([dict(req, nums=1)])
+        ops.append(("filter", {"uid": uid, "ns": "default", "name": uid, "annotations": annos, "containers": ctrs, "n_init": 0}))
+        live.append(uid)
+        if live and rng.random() < 0.35:
+            ops.append(("delete", live.pop(rng.randrange(len(live)))))
+    return {"node_policy": "binpack", "gpu_policy": "spread"}, nodes, ops
+
+
+@pytest.mark.gpu
+def test_plain_vendors_gpu_parity():
+    cfg, nodes, ops = _cluster(60, 900)
+    ref, ref_snap = parity.run_oracle(cfg, nodes, ops)
+    got, snap = parity.run_engine(cfg, nodes, ops, chunk=300)
+    assert parity.compare(ops, ref, got, ref_snap, snap) == []
+    fits = {}
+    for (kind, arg), r in zip(ops, ref):
+        if kind == "filter" and r["status"] == abi.HS_FIT:
+            k = arg["containers"][0][0]["type"]
+            fits[k] = fits.get(k, 0) + 1
+    assert fits.get("Biren", 0) > 20 and fits.get("MR-V100", 0) > 20 and fits.get("BI-V150", 0) > 20 and "MR-V50" not in fits
+    sample = next(r for (kind, arg), r in zip(ops, ref) if kind == "filter" and r["status"] == abi.HS_FIT and arg["containers"][0][0]["type"] == "Biren")
+    assert "hami.io/Biren-devices-allocated" in sample["annotations"] and "hami.io/Biren-devices-to-allocate" in sample["annotations"]

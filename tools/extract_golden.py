@@ -332,6 +332,8 @@ IDENTS = {
     "Ascend910CType": "Ascend910C", "Ascend910Prefix": "Ascend910",
     "VNPUModeAnnotation": "huawei.com/vnpu-mode", "VNPUModeHamiCore": "hami-core",
     "VNPUNodeSelectorAnnotation": "hami-vnpu-core",
+    "BirenDevice": "Biren", "BirenCommonWord": "Biren",
+    "BirenUseUUID": "birentech.com/use-gpuuuid", "BirenNoUseUUID": "birentech.com/nouse-gpuuuid",
 }
 for k in list(IDENTS):
     if k.startswith("util."):
@@ -433,6 +435,9 @@ TABLES = [
     ("marshal_node_devices", "pkg/device/devices_test.go", "TestMarshalNodeDevices", "tests"),
     # namespace quota: quota = limits.nvidia.com/gpumem 2048 in namespace "default" (device_test.go:1324-1339)
     ("nvidia_fit_quota", "pkg/device/nvidia/device_test.go", "TestFitQuota", "tests"),
+    # vendors with a plain Fit
+    ("iluvatar_fit", "pkg/device/iluvatar/device_test.go", "Test_Fit", "tests"),
+    ("biren_fit", "pkg/device/biren/device_test.go", "TestDevices_Fit", "tests"),
 ]
 
 
