@@ -210,6 +210,34 @@ __device__ __forceinline__ unsigned long long slot_argbest(const KernelArgs& ka,
   return *s_win;
 }
 
+// The same slot barrier in two halves (one GPU only), so that work whose result is needed only AFTER the winner is
+// known — the winner-side full evaluation — runs while the arrivals travel: slot_arrive folds the CTA's key in and
+// signals, slot_wait polls.  Every thread calls both; nothing else may touch s_red / s_win in between.
+__device__ __forceinline__ void slot_arrive(OpSync* slot, unsigned long long warp_key, unsigned long long* s_red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  if (lane == 0) s_red[warp] = warp_key;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned long long v = lane < nwarps ? s_red[lane] : 0ull;
+    v = warp_max_u64(v);
+    if (lane == 0) {
+      if (v) atomicMax(&slot->best, v);
+      asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
+    }
+  }
+}
+__device__ __forceinline__ unsigned long long slot_wait(OpSync* slot, unsigned long long* s_win) {
+  if (threadIdx.x == 0) {
+    unsigned long long best = 0, cnt;
+    do {
+      asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
+    } while ((uint32_t)cnt < gridDim.x);
+    *s_win = best;
+  }
+  __syncthreads();
+  return *s_win;
+}
+
 // ---- request staging: the next op's 160 B record is prefetched with cp.async while the current
 // op is evaluated (two shared-memory buffers).
 __device__ __forceinline__ void prefetch_op(const DevPod* src, DevPod* dst) {
@@ -327,7 +355,11 @@ hs_decide_kernel(const KernelArgs ka) {
     const bool fast = pod.fast != 0;
     // streaming mode only: in resident mode the full evaluation runs in parallel everywhere, so the winner can
     // commit straight after the barrier (measured: deferring it to the winner lengthens the critical path)
-    const bool lite = fast && !resident && !((pod.flags & PF_NUMA_ASSERT) && pod.e0.vendor == HV_NVIDIA);
+    // Without numa-bind the VERDICT needs no score/sort (fast_fit_lite).  Streaming mode: the winner's warp runs the
+    // full evaluation afterwards.  Resident mode on one GPU: every group that fits runs it while the barrier's
+    // arrivals are in flight (`deferred`), so the winner still commits straight after the barrier.
+    const bool lite = fast && !((pod.flags & PF_NUMA_ASSERT) && pod.e0.vendor == HV_NVIDIA) && (!resident || ka.world <= 1);
+    const bool deferred = lite && resident;
     const DevEntry* ent = &pod.e0;
     if (pod.n_entries > 1) {     // general path with several entries: fetch them from the pool
       const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.entries + pod.entry_off);
@@ -420,7 +452,15 @@ hs_decide_kernel(const KernelArgs ka) {
     // ---- arg-best: warp shuffle, one atomicMax per CTA, ONE grid barrier -----------------------
     const unsigned long long bk = warp_max_u64(my_key);
     TICK(3);
-    const unsigned long long win = slot_argbest(ka, ka.sync + r, barriers, bk, s_red, &s_win);
+    unsigned long long win;
+    if (ka.world <= 1) {
+      slot_arrive(ka.sync + r, bk, s_red);
+      if (deferred && __any_sync(FULL, my_key != 0ull))     // warp-uniform: fast_fit is a whole-warp collective
+        fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
+      win = slot_wait(ka.sync + r, &s_win);
+    } else {
+      win = slot_argbest(ka, ka.sync + r, barriers, bk, s_red, &s_win);
+    }
     barriers++;
     TICK(4);
 
@@ -440,7 +480,7 @@ hs_decide_kernel(const KernelArgs ka) {
         }
       }
       if (fast) {
-        if ((lite || !resident) && __any_sync(FULL, mine)) {
+        if (!resident && __any_sync(FULL, mine)) {
           // the sweep only established THAT the node fits (or ran on streamed registers): the winner's warp
           // now runs the full evaluation to learn which devices (collectives → the whole warp takes part)
           if (!resident) {
