@@ -315,6 +315,38 @@ int32_t hs_shard_init(hs_handle* h, int32_t rank, int32_t world, const void* uni
 int32_t hs_shard_mailbox(hs_handle* h, void* out64);
 int32_t hs_shard_connect(hs_handle* h, const void* handles64, int32_t world);
 
+/* ---- request extraction: device.Resourcereqs for one container (pkg/device/devices.go:639-691)
+ * over <vendor>.GenerateResourceRequests (nvidia/device.go:520-600, hygon/device.go:168-239,
+ * cambricon/device.go:250-305, ascend/device.go:303-378).  A resource.Quantity arrives as the three views the
+ * reference reads: AsInt64() (+ ok), Value() (rounded up) and Sign().  Pure host code, needs no handle.            */
+typedef struct hs_quantity {
+  const char* name;         /* resource name, e.g. "nvidia.com/gpumem"      */
+  int64_t     as_int64;     /* Quantity.AsInt64() value                     */
+  uint8_t     as_int64_ok;  /* … and its ok flag                            */
+  int64_t     value;        /* Quantity.Value()                             */
+  int8_t      sign;         /* Quantity.Sign()                              */
+} hs_quantity;
+typedef struct hs_container_resources {
+  const hs_quantity* limits;   uint32_t n_limits;     /* ctr.Resources.Limits   */
+  const hs_quantity* requests; uint32_t n_requests;   /* ctr.Resources.Requests */
+} hs_container_resources;
+enum { HS_REQ_NVIDIA = 0, HS_REQ_DCU = 1, HS_REQ_MLU = 2, HS_REQ_ASCEND = 3 };
+typedef struct hs_vendor_resources {
+  const char* common_word;             /* becomes the request's key and Type                                  */
+  int32_t     kind;                    /* HS_REQ_*: whose GenerateResourceRequests                             */
+  const char* count_name;              /* ResourceCountName, e.g. "nvidia.com/gpu"                             */
+  const char* memory_name;             /* ResourceMemoryName                                                   */
+  const char* memory_percentage_name;  /* NVIDIA only                                                          */
+  const char* cores_name;              /* ResourceCoreName; NULL / "" = none (Ascend)                          */
+  int32_t     default_memory;          /* NVIDIA DefaultMemory                                                 */
+  int32_t     default_cores;           /* NVIDIA DefaultCores                                                  */
+  int32_t     memory_factor;           /* MemoryFactor (MLU: 256)                                              */
+} hs_vendor_resources;
+/* Fills out[] with the container's requests whose Nums > 0 (key == type == common_word, pointers borrowed from
+ * `vendors`), in vendor order; returns how many there are (may exceed cap).                                   */
+int32_t hs_generate_requests(const hs_vendor_resources* vendors, uint32_t n_vendors, const hs_container_resources* ctr,
+                             hs_container_request* out, uint32_t cap);
+
 /* ---- ingest: the data formats that keep the HBM inventory true ---------------------------
  * The reference learns a node's devices from register annotations and a pod's committed allocation from its
  * "<vendor>-devices-allocated" annotations; these entry points take the annotation STRINGS.                */

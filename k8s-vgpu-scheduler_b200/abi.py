@@ -94,6 +94,23 @@ class hs_ascend_config(C.Structure):
                 ("templates", C.POINTER(hs_ascend_template)), ("n_templates", C.c_uint32)]
 
 
+class hs_quantity(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("as_int64", C.c_int64), ("as_int64_ok", C.c_uint8), ("value", C.c_int64), ("sign", C.c_int8)]
+
+
+class hs_container_resources(C.Structure):
+    _fields_ = [("limits", C.POINTER(hs_quantity)), ("n_limits", C.c_uint32), ("requests", C.POINTER(hs_quantity)), ("n_requests", C.c_uint32)]
+
+
+class hs_vendor_resources(C.Structure):
+    _fields_ = [("common_word", C.c_char_p), ("kind", C.c_int32), ("count_name", C.c_char_p), ("memory_name", C.c_char_p),
+                ("memory_percentage_name", C.c_char_p), ("cores_name", C.c_char_p), ("default_memory", C.c_int32),
+                ("default_cores", C.c_int32), ("memory_factor", C.c_int32)]
+
+
+HS_REQ_NVIDIA, HS_REQ_DCU, HS_REQ_MLU, HS_REQ_ASCEND = 0, 1, 2, 3
+
+
 class hs_vendor_config(C.Structure):
     _fields_ = [("common_word", C.c_char_p), ("fit_kind", C.c_int32), ("use_uuid_key", C.c_char_p),
                 ("nouse_uuid_key", C.c_char_p), ("to_allocate_key", C.c_char_p), ("allocated_key", C.c_char_p)]

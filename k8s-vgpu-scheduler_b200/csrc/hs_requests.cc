@@ -1,0 +1,123 @@
+// hs_requests.cc — request extraction: device.Resourcereqs for one container
+// (pkg/device/devices.go:639-691) over the vendors' GenerateResourceRequests:
+//   NVIDIA  pkg/device/nvidia/device.go:520-600     DCU     pkg/device/hygon/device.go:168-239
+//   MLU     pkg/device/cambricon/device.go:250-305  Ascend  pkg/device/ascend/device.go:303-378
+// Input = the container's resource limits / requests with the three views of a resource.Quantity the reference
+// uses (AsInt64, Value, Sign), output = the ContainerDeviceRequest list hs_pod carries.  Plain host code.
+#include <stdint.h>
+#include <string.h>
+
+#include "../../include/hami_sched.h"
+
+namespace {
+
+const int64_t kMaxInt32 = 2147483647;
+
+const hs_quantity* lookup(const hs_container_resources* c, const char* name) {
+  if (!name || !name[0]) return nullptr;
+  for (uint32_t i = 0; i < c->n_limits; i++)                  // Limits first, then Requests
+    if (c->limits[i].name && strcmp(c->limits[i].name, name) == 0) return &c->limits[i];
+  for (uint32_t i = 0; i < c->n_requests; i++)
+    if (c->requests[i].name && strcmp(c->requests[i].name, name) == 0) return &c->requests[i];
+  return nullptr;
+}
+
+// returns false for the zero-value ContainerDeviceRequest{}
+bool generate(const hs_vendor_resources& v, const hs_container_resources* c, hs_container_request& r) {
+  const hs_quantity* cnt = lookup(c, v.count_name);
+  if (!cnt || !cnt->as_int64_ok) return false;
+  const int64_t n = cnt->as_int64;
+  const int64_t factor = v.memory_factor > 1 ? v.memory_factor : 1;
+  const hs_quantity* mem = lookup(c, v.memory_name);
+  const hs_quantity* core = lookup(c, v.cores_name);
+  int64_t memnum = 0;
+  int32_t mempnum, corenum;
+  switch (v.kind) {
+    case HS_REQ_NVIDIA: {
+      if (mem) {
+        if (!mem->as_int64_ok || mem->as_int64 < 0 || mem->as_int64 > kMaxInt32 / factor) return false;
+        memnum = mem->as_int64 * factor;
+      }
+      mempnum = 101;                                          // "unset" sentinel (nvidia/device.go:551)
+      const hs_quantity* pct = lookup(c, v.memory_percentage_name);
+      if (pct && pct->as_int64_ok) {
+        int64_t p = pct->as_int64 > 100 ? 100 : pct->as_int64;
+        mempnum = p > 0 ? (int32_t)p : 101;
+      }
+      if (mempnum == 101 && memnum == 0) {
+        if (v.default_memory != 0) memnum = v.default_memory;
+        else mempnum = 100;
+      }
+      corenum = v.default_cores;
+      if (core && core->as_int64_ok) corenum = (int32_t)core->as_int64;
+      break;
+    }
+    case HS_REQ_DCU: {
+      if (n <= 0 || n > kMaxInt32) return false;
+      if (mem && mem->as_int64_ok) {
+        if (mem->as_int64 < 0 || mem->as_int64 > kMaxInt32) return false;
+        memnum = mem->as_int64;
+        if (v.memory_factor > 1) { memnum *= v.memory_factor; if (memnum > kMaxInt32) return false; }
+      }
+      corenum = 100;
+      if (core && core->as_int64_ok) {
+        if (core->as_int64 < 0 || core->as_int64 > kMaxInt32) return false;
+        corenum = (int32_t)core->as_int64;
+      }
+      mempnum = memnum == 0 ? 100 : 0;
+      break;
+    }
+    case HS_REQ_MLU: {
+      if (mem) {
+        if (!mem->as_int64_ok || mem->as_int64 < 0 || mem->as_int64 > kMaxInt32 / factor) return false;
+        memnum = mem->as_int64 * factor;
+      }
+      corenum = 100;
+      if (core && core->as_int64_ok) corenum = (int32_t)core->as_int64;
+      mempnum = memnum == 0 ? 100 : 0;
+      break;
+    }
+    case HS_REQ_ASCEND: {
+      if (n <= 0 || n > kMaxInt32) return false;
+      if (mem) {
+        if (mem->sign < 0) return false;                      // -1m has no int64 form: reject by sign first
+        if (mem->as_int64_ok) {
+          if (mem->as_int64 > kMaxInt32) return false;
+          memnum = mem->as_int64;
+          if (v.memory_factor > 1) { memnum *= v.memory_factor; if (memnum > kMaxInt32) return false; }
+        }
+      }
+      corenum = 0;
+      if (core) {
+        if (core->value < 0 || core->value > kMaxInt32) return false;   // Quantity.Value(), rounded up
+        corenum = (int32_t)core->value;
+      }
+      mempnum = memnum == 0 ? 100 : 0;
+      break;
+    }
+    default:
+      return false;
+  }
+  r.key = v.common_word;
+  r.type = v.common_word;
+  r.nums = (int32_t)n;
+  r.memreq = (int32_t)memnum;
+  r.mempct = mempnum;
+  r.coresreq = corenum;
+  return true;
+}
+
+}  // namespace
+
+extern "C" int32_t hs_generate_requests(const hs_vendor_resources* vendors, uint32_t n_vendors, const hs_container_resources* ctr,
+                                        hs_container_request* out, uint32_t cap) {
+  if ((!vendors && n_vendors) || !ctr || (!out && cap)) return HS_ERR_INVALID;
+  uint32_t k = 0;
+  for (uint32_t i = 0; i < n_vendors; i++) {
+    hs_container_request r;
+    if (!generate(vendors[i], ctr, r) || r.nums <= 0) continue;   // devices.go:660-663: only requests with Nums > 0 are kept
+    if (k < cap) out[k] = r;
+    k++;
+  }
+  return (int32_t)k;
+}

@@ -1,0 +1,242 @@
+"""Request extraction: hs_generate_requests — device.Resourcereqs for one container over the
+vendors' GenerateResourceRequests — against the reference's own tables:
+
+  tests/golden/nvidia_generate_requests.json        nvidia/device_test.go TestGenerateResourceRequests (15 cases)
+  tests/golden/hygon_generate_requests*.json        hygon/device_test.go Test_GenerateResourceRequests (+ OutOfRangeValues)
+  tests/golden/cambricon_generate_requests.json     cambricon/device_test.go Test_GenerateResourceRequests
+  tests/golden/ascend_generate_requests*.json       ascend/device_test.go Test_GenerateResourceRequests (+ OutOfRangeValues)
+plus the MemoryFactor / DefaultMemory cases of nvidia/device_test.go:1995-2045 and a seeded differential run against
+the Python restatement below (test infrastructure, written from the reference independently of the C++).
+Host code only: no GPU needed.
+"""
+import ctypes as C
+import json
+import os
+import random
+import re
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import k8s_vgpu_scheduler_b200.engine as eng  # noqa: E402
+from k8s_vgpu_scheduler_b200 import abi  # noqa: E402
+
+MAXI32 = 2 ** 31 - 1
+SUFFIX = {"": 1, "k": 10 ** 3, "M": 10 ** 6, "G": 10 ** 9, "T": 10 ** 12, "Ki": 2 ** 10, "Mi": 2 ** 20, "Gi": 2 ** 30, "Ti": 2 ** 40}
+
+NVIDIA = dict(word="NVIDIA", kind=abi.HS_REQ_NVIDIA, count="nvidia.com/gpu", mem="nvidia.com/gpumem",
+              pct="nvidia.com/gpumem-percentage", cores="nvidia.com/gpucores", default_mem=0, default_cores=0, factor=1)
+DCU = dict(word="DCU", kind=abi.HS_REQ_DCU, count="hygon.com/dcunum", mem="hygon.com/dcumem", pct=None, cores="hygon.com/dcucores",
+           default_mem=0, default_cores=0, factor=1)
+MLU = dict(word="MLU", kind=abi.HS_REQ_MLU, count="cambricon.com/mlu", mem="cambricon.com/mlu.smlu.vmemory", pct=None,
+           cores="cambricon.com/mlu.smlu.vcore", default_mem=0, default_cores=0, factor=256)
+ASCEND_910A = dict(word="Ascend910A", kind=abi.HS_REQ_ASCEND, count="huawei.com/Ascend910A", mem="huawei.com/Ascend910A-memory",
+                   pct=None, cores=None, default_mem=0, default_cores=0, factor=1)
+ASCEND_CORE = dict(word="Ascend910B3", kind=abi.HS_REQ_ASCEND, count="huawei.com/Ascend910B3", mem="huawei.com/Ascend910B3-memory",
+                   pct=None, cores="huawei.com/Ascend910B3-core", default_mem=0, default_cores=0, factor=1)
+
+
+def quantity(q):
+    """resource.Quantity as the three views the reference reads: (AsInt64 value, ok, Value() rounded up, Sign())."""
+    if isinstance(q, int):
+        return q, True, q, (q > 0) - (q < 0)
+    s = q["_quantity"]
+    m = re.match(r"^([+-]?)(\d+)(?:\.(\d+))?(m|k|M|G|T|Ki|Mi|Gi|Ti)?$", s)
+    assert m, s
+    sign = -1 if m.group(1) == "-" else 1
+    whole, frac, suf = int(m.group(2)), m.group(3), m.group(4) or ""
+    if suf == "m":
+        milli = sign * (whole * 1000 + int((frac or "0").ljust(3, "0")[:3])) if frac else sign * whole
+        exact = milli % 1000 == 0
+        val = -((-milli) // 1000) if milli < 0 else -(-milli // 1000)       # round away from zero like Value()
+        return (milli // 1000 if exact else 0), exact, val, (milli > 0) - (milli < 0)
+    if frac is not None:          # decimal-form literals are held as inf.Dec: AsInt64 reports !ok (device_test "16.0Gi")
+        v = sign * int(round(float("%d.%s" % (whole, frac)) * SUFFIX[suf]))
+        return 0, False, v, (v > 0) - (v < 0)
+    v = sign * whole * SUFFIX[suf]
+    return v, True, v, (v > 0) - (v < 0)
+
+
+def oracle_generate(v, limits, requests):
+    """GenerateResourceRequests restated from nvidia/device.go:520-600, hygon/device.go:168-239,
+    cambricon/device.go:250-305, ascend/device.go:303-378.  Returns the request dict or None (zero value)."""
+    def get(name):
+        if not name:
+            return None
+        return limits.get(name, requests.get(name))
+    cnt = get(v["count"])
+    if cnt is None or not cnt[1]:
+        return None
+    n = cnt[0]
+    factor = max(v["factor"], 1)
+    mem, core = get(v["mem"]), get(v["cores"])
+    memnum = 0
+    wrap = lambda x: ((x + 2 ** 31) % 2 ** 32) - 2 ** 31   # noqa: E731  int32(x)
+    if v["kind"] == abi.HS_REQ_NVIDIA:
+        if mem is not None:
+            if not mem[1] or mem[0] < 0 or mem[0] > MAXI32 // factor:
+                return None
+            memnum = mem[0] * factor
+        pctn = 101
+        pct = get(v["pct"])
+        if pct is not None and pct[1]:
+            p = min(pct[0], 100)
+            pctn = p if p > 0 else 101
+        if pctn == 101 and memnum == 0:
+            if v["default_mem"]:
+                memnum = v["default_mem"]
+            else:
+                pctn = 100
+        cores = v["default_cores"]
+        if core is not None and core[1]:
+            cores = wrap(core[0])
+    elif v["kind"] == abi.HS_REQ_DCU:
+        if n <= 0 or n > MAXI32:
+            return None
+        if mem is not None and mem[1]:
+            if mem[0] < 0 or mem[0] > MAXI32:
+                return None
+            memnum = mem[0] * (v["factor"] if v["factor"] > 1 else 1)
+            if memnum > MAXI32:
+                return None
+        cores = 100
+        if core is not None and core[1]:
+            if core[0] < 0 or core[0] > MAXI32:
+                return None
+            cores = core[0]
+        pctn = 100 if memnum == 0 else 0
+    elif v["kind"] == abi.HS_REQ_MLU:
+        if mem is not None:
+            if not mem[1] or mem[0] < 0 or mem[0] > MAXI32 // factor:
+                return None
+            memnum = mem[0] * factor
+        cores = 100
+        if core is not None and core[1]:
+            cores = wrap(core[0])
+        pctn = 100 if memnum == 0 else 0
+    else:
+        if n <= 0 or n > MAXI32:
+            return None
+        if mem is not None:
+            if mem[3] < 0:
+                return None
+            if mem[1]:
+                if mem[0] > MAXI32:
+                    return None
+                memnum = mem[0] * (v["factor"] if v["factor"] > 1 else 1)
+                if memnum > MAXI32:
+                    return None
+        cores = 0
+        if core is not None:
+            if core[2] < 0 or core[2] > MAXI32:
+                return None
+            cores = core[2]
+        pctn = 100 if memnum == 0 else 0
+    return {"Nums": wrap(n), "Type": v["word"], "Memreq": wrap(memnum), "MemPercentagereq": pctn, "Coresreq": cores}
+
+
+def product_generate(vendors, limits, requests):
+    L = eng.lib()
+    L.hs_generate_requests.argtypes = [C.POINTER(abi.hs_vendor_resources), C.c_uint32, C.POINTER(abi.hs_container_resources),
+                                       C.POINTER(abi.hs_container_request), C.c_uint32]
+    va = (abi.hs_vendor_resources * len(vendors))(*[
+        abi.hs_vendor_resources(abi._b(v["word"]), v["kind"], abi._b(v["count"]), abi._b(v["mem"]), abi._b(v["pct"]), abi._b(v["cores"]),
+                                v["default_mem"], v["default_cores"], v["factor"]) for v in vendors])
+
+    def arr(d):
+        a = (abi.hs_quantity * max(len(d), 1))()
+        for i, (k, q) in enumerate(d.items()):
+            a[i] = abi.hs_quantity(abi._b(k), q[0], 1 if q[1] else 0, q[2], q[3])
+        return a
+    la, ra = arr(limits), arr(requests)
+    ctr = abi.hs_container_resources(la, len(limits), ra, len(requests))
+    out = (abi.hs_container_request * 16)()
+    n = L.hs_generate_requests(va, len(vendors), C.byref(ctr), out, 16)
+    assert n >= 0
+    return [{"Nums": out[i].nums, "Type": out[i].type.decode(), "Memreq": out[i].memreq, "MemPercentagereq": out[i].mempct,
+             "Coresreq": out[i].coresreq, "key": out[i].key.decode()} for i in range(n)]
+
+
+def resources(case):
+    ctr = case.get("ctr") or case.get("args") or {}
+    res = ctr.get("Resources", {}) if isinstance(ctr, dict) else {}
+    conv = lambda d: {k: quantity(q) for k, q in d.items()} if isinstance(d, dict) else {}   # noqa: E731
+    return conv(res.get("Limits", {})), conv(res.get("Requests", {}))
+
+
+def want_of(case):
+    w = case["want"]
+    if not isinstance(w, dict) or w.get("Nums", 0) <= 0:
+        return None
+    return {k: w.get(k, 0) for k in ("Nums", "Memreq", "MemPercentagereq", "Coresreq")} | {"Type": w["Type"]}
+
+
+def strip(r):
+    return None if r is None else {k: r[k] for k in ("Nums", "Type", "Memreq", "MemPercentagereq", "Coresreq")}
+
+
+TABLES = [("nvidia_generate_requests", NVIDIA, 15), ("hygon_generate_requests", DCU, 5), ("hygon_generate_requests_range", DCU, 2),
+          ("cambricon_generate_requests", MLU, 6), ("ascend_generate_requests", ASCEND_910A, 3),
+          ("ascend_generate_requests_range", ASCEND_CORE, 7)]
+
+
+@pytest.mark.parametrize("name,vendor,count", TABLES, ids=[t[0] for t in TABLES])
+def test_generate_requests_golden(name, vendor, count):
+    cases = json.load(open(os.path.join(ROOT, "tests", "golden", name + ".json")))["cases"]
+    assert len(cases) == count
+    for c in cases:
+        limits, requests = resources(c)
+        want = want_of(c)
+        ref = oracle_generate(vendor, limits, requests)
+        ref = ref if ref and ref["Nums"] > 0 else None
+        assert strip(ref) == want, ("oracle", c["name"])
+        got = product_generate([vendor], limits, requests)
+        assert (strip(got[0]) if got else None) == want, ("product", c["name"])
+        if got:
+            assert got[0]["key"] == vendor["word"]
+
+
+def test_nvidia_memory_factor_and_default_memory():
+    # nvidia/device_test.go:1995-2018 (MemoryFactor 1000: 4 -> 4000) and :2020-2045 (DefaultMemory applies when neither is set)
+    q = lambda n: (n, True, n, 1)   # noqa: E731
+    v = dict(NVIDIA, factor=1000)
+    got = product_generate([v], {"nvidia.com/gpu": q(1), "nvidia.com/gpumem": q(4)}, {})
+    assert strip(got[0]) == strip(oracle_generate(v, {"nvidia.com/gpu": q(1), "nvidia.com/gpumem": q(4)}, {}))
+    assert got[0]["Memreq"] == 4000 and got[0]["MemPercentagereq"] == 101
+    v = dict(NVIDIA, default_mem=3000, default_cores=30)
+    got = product_generate([v], {"nvidia.com/gpu": q(2)}, {})
+    assert (got[0]["Memreq"], got[0]["MemPercentagereq"], got[0]["Coresreq"], got[0]["Nums"]) == (3000, 101, 30, 2)
+
+
+def test_resourcereqs_keeps_only_positive_counts_in_vendor_order():
+    q = lambda n: (n, True, n, (n > 0) - (n < 0))   # noqa: E731
+    vendors = [NVIDIA, DCU, MLU, ASCEND_CORE]
+    limits = {"nvidia.com/gpu": q(2), "hygon.com/dcunum": q(0), "cambricon.com/mlu": q(1), "cambricon.com/mlu.smlu.vmemory": q(10),
+              "huawei.com/Ascend910B3": q(-1)}
+    got = product_generate(vendors, limits, {})
+    assert [g["Type"] for g in got] == ["NVIDIA", "MLU"] and got[1]["Memreq"] == 2560
+
+
+def test_product_matches_restatement_on_random_containers():
+    rng = random.Random(42)
+    vendors = [NVIDIA, dict(NVIDIA, word="NV2", factor=4, default_mem=777, default_cores=5), DCU, dict(DCU, word="DCU2", factor=3),
+               MLU, ASCEND_910A, ASCEND_CORE, dict(ASCEND_CORE, word="AscF", factor=2)]
+    names = sorted({v[k] for v in vendors for k in ("count", "mem", "pct", "cores") if v[k]})
+    pool = [0, 1, 2, 8, -1, -100, 100, 101, 150, 4096, 2 ** 31 - 1, 2 ** 31, 2200000000, 2 ** 32 + 50, 8388607, 8388608,
+            {"_quantity": "16Gi"}, {"_quantity": "16.0Gi"}, {"_quantity": "-1m"}, {"_quantity": "1500m"}, {"_quantity": "2000m"}]
+    kept = 0
+    for _ in range(4000):
+        limits = {n: quantity(rng.choice(pool)) for n in names if rng.random() < 0.45}
+        requests = {n: quantity(rng.choice(pool)) for n in names if rng.random() < 0.25}
+        want = []
+        for v in vendors:
+            r = oracle_generate(v, limits, requests)
+            if r and r["Nums"] > 0:
+                want.append(strip(r))
+        got = [strip(g) for g in product_generate(vendors, limits, requests)]
+        assert got == want, (limits, requests)
+        kept += len(want)
+    assert kept > 2000

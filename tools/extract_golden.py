@@ -436,9 +436,21 @@ TABLES = [
     # namespace quota: quota = limits.nvidia.com/gpumem 2048 in namespace "default" (device_test.go:1324-1339)
     ("nvidia_fit_quota", "pkg/device/nvidia/device_test.go", "TestFitQuota", "tests"),
     # vendors with a plain Fit
+    # request extraction: <vendor>.GenerateResourceRequests
+    ("nvidia_generate_requests", "pkg/device/nvidia/device_test.go", "TestGenerateResourceRequests", "tests"),
+    ("hygon_generate_requests", "pkg/device/hygon/device_test.go", "Test_GenerateResourceRequests", "tests"),
+    ("hygon_generate_requests_range", "pkg/device/hygon/device_test.go", "Test_GenerateResourceRequests_OutOfRangeValues", "tests"),
+    ("cambricon_generate_requests", "pkg/device/cambricon/device_test.go", "Test_GenerateResourceRequests", "tests"),
+    ("ascend_generate_requests", "pkg/device/ascend/device_test.go", "Test_GenerateResourceRequests", "tests"),
+    ("ascend_generate_requests_range", "pkg/device/ascend/device_test.go", "Test_GenerateResourceRequests_OutOfRangeValues", "tests"),
     ("iluvatar_fit", "pkg/device/iluvatar/device_test.go", "Test_Fit", "tests"),
     ("biren_fit", "pkg/device/biren/device_test.go", "TestDevices_Fit", "tests"),
 ]
+
+
+SOURCE_PATCHES = {
+    ("pkg/device/nvidia/device_test.go", "TestGenerateResourceRequests"): [("int64(1)<<32+50", "4294967346")],
+}
 
 
 def main():
@@ -451,6 +463,8 @@ def main():
             src = open(path).read()
             body = find_func(src, func)
             line = src[:src.index(body)].count("\n") + 1
+            for old, new in SOURCE_PATCHES.get((rel, func), []):   # Go expressions the literal parser does not evaluate
+                body = body.replace(old, new)
             table = extract_table(body, var)
         except (KeyError, SyntaxError, FileNotFoundError) as e:
             print("SKIP %-28s %s:%s  (%s: %s)" % (name, rel, func, type(e).__name__, e))
