@@ -139,6 +139,16 @@ def algorithmic_bytes(ops, n_nodes):
     return total
 
 
+def decide_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE hs_decide_kernel launch, from the committed ncu --set full
+    capture (profiles/r01_decide_full_final.json); None when the summary is missing."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_decide_full_final.json")) as f:
+            return int(json.load(f)["dram_bytes_per_launch"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def run_ours(args):
     import torch  # device memory / streams / distributed are torch's job on the multi-GPU path
     import k8s_vgpu_scheduler_b200.engine as eng
@@ -223,7 +233,7 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                     "frac": round(achieved / peak, 4), "traffic": decide_traffic(), "peak_source": peak_src,
                      "kernel": "hs_decide_kernel",
                      "note": "algorithmic bytes = decisions x (N x 8 x 32 B + N x 128 B topology tile + nums x 16 B); "
                              "at 5k nodes the loop is barrier-latency bound, HBM evidence is the scan probe (profiles/)"},
