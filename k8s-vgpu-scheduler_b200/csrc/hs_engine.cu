@@ -1410,7 +1410,10 @@ void hs_destroy(hs_handle* h) {
   if (h->d_tot) cudaFree(h->d_tot);
   h->b_pods.release(); h->b_entries.release(); h->b_uuid.release(); h->b_rel.release(); h->b_dec.release();
   h->b_alloc.release(); h->b_delta.release(); h->b_best.release(); h->b_fail.release(); h->b_counters.release();
-  h->b_candpos.release(); h->b_timing.release();
+  h->b_candpos.release(); h->b_timing.release(); h->b_quota.release();
+  for (int p = 0; p < 8; p++)        // peer mailboxes opened with cudaIpcOpenMemHandle; our own is a plain allocation
+    if (h->mbox_peer[p] && h->mbox_peer[p] != h->d_mbox) cudaIpcCloseMemHandle(h->mbox_peer[p]);
+  if (h->d_mbox) cudaFree(h->d_mbox);
   if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
