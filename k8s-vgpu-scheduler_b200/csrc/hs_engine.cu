@@ -850,7 +850,8 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
       CUDA_OK(h, cudaMemcpyAsync(h->b_counters.d, h->b_counters.h, 8 * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
   }
-  if (alloc_base) CUDA_OK(h, cudaMemcpy(h->b_alloc.h, h->b_alloc.d, (size_t)std::min(alloc_base, alloc_cap) * sizeof(DevAlloc), cudaMemcpyDeviceToHost));
+  (void)alloc_base;   // rows sit at each op's own alloc_base (a host-made prefix sum), not behind a device cursor
+  if (alloc_cap) CUDA_OK(h, cudaMemcpy(h->b_alloc.h, h->b_alloc.d, (size_t)alloc_cap * sizeof(DevAlloc), cudaMemcpyDeviceToHost));
   CUDA_OK(h, cudaMemcpy(h->b_delta.h, h->b_delta.d, (size_t)n_ops * HS_D * sizeof(int4), cudaMemcpyDeviceToHost));
   return HS_OK;
 }
@@ -1208,6 +1209,17 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
     p.rel_node = it->second.node;
     p.rel_off = (int32_t)rel.size();
     for (int d = 0; d < HS_D; d++) rel.push_back(it->second.delta[d]);
+    {   // the same rows inside the op record (RelDelta over e0): the resident owner needs no second fetch
+      RelDelta rd[HS_D];
+      bool fits = true;
+      for (int d = 0; d < HS_D; d++) {
+        const int4& v = it->second.delta[d];
+        if (v.x < 0 || v.x > 65535 || v.z < -32768 || v.z > 32767) fits = false;
+        rd[d].mem = v.y; rd[d].cores = (int16_t)v.z; rd[d].slots = (uint16_t)v.x;
+      }
+      if (!fits) { h->err = "release delta outside the op record's range"; return false; }
+      memcpy(&p.e0, rd, sizeof rd);
+    }
     rel_ns = it->second.ns;
     h->pods.erase(it);
   }
@@ -1285,6 +1297,7 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
     c.pod.entry_off = (uint32_t)entries.size();
     entries.insert(entries.end(), c.entries.begin(), c.entries.end());
     c.meta.user_op = (int)i;
+    c.pod.alloc_base = alloc_cap;
     pods.push_back(c.pod);
     metas.push_back(c.meta);
     if (!h->dry_run) in_batch[uid] = (int)pods.size() - 1;

@@ -238,10 +238,14 @@ __device__ __forceinline__ unsigned long long slot_wait(OpSync* slot, unsigned l
   return *s_win;
 }
 
-// ---- request staging: the next op's 160 B record is prefetched with cp.async while the current
-// op is evaluated (two shared-memory buffers).
-__device__ __forceinline__ void prefetch_op(const DevPod* src, DevPod* dst) {
-  if (threadIdx.x < sizeof(DevPod) / 16) {
+// ---- request staging: op records (160 B) are prefetched with cp.async into a ring of HS_PF shared-memory
+// buffers, HS_PF-1 ops ahead: a RELEASE op is only a few hundred cycles long, shorter than the L2 latency of the
+// next record, so a distance of one op stalled every short op on its successor's fetch.  Every op position issues
+// exactly one commit_group (an empty one past the end of the stream), so "all but the HS_PF-2 newest groups are
+// complete" means "op r has landed".
+#define HS_PF 4
+__device__ __forceinline__ void prefetch_op(const DevPod* src, DevPod* dst, bool valid) {
+  if (valid && threadIdx.x < sizeof(DevPod) / 16) {
     const uint32_t s = (uint32_t)__cvta_generic_to_shared(reinterpret_cast<char*>(dst) + threadIdx.x * 16);
     const char* g = reinterpret_cast<const char*>(src) + threadIdx.x * 16;
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(g) : "memory");
@@ -249,13 +253,14 @@ __device__ __forceinline__ void prefetch_op(const DevPod* src, DevPod* dst) {
   asm volatile("cp.async.commit_group;" ::: "memory");
 }
 __device__ __forceinline__ void prefetch_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void prefetch_wait_oldest() { asm volatile("cp.async.wait_group %0;" ::"n"(HS_PF - 2) : "memory"); }
 
 
 #define FULL 0xffffffffu
 
 extern "C" __global__ void __launch_bounds__(512, 1)
 hs_decide_kernel(const KernelArgs ka) {
-  __shared__ __align__(16) DevPod s_op[2];
+  __shared__ __align__(16) DevPod s_op[HS_PF];
   __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
   __shared__ unsigned long long s_red[32];
   __shared__ unsigned long long s_win;
@@ -288,17 +293,17 @@ hs_decide_kernel(const KernelArgs ka) {
   uint32_t fail_count = 0;     // no-fit decisions so far: identical in every thread
   uint32_t barriers = 0;       // arg-best exchanges so far in this launch: identical in every thread (and rank)
   int r = ka.op_begin;
-  if (r < ka.n_ops) prefetch_op(ka.pods + r, &s_op[0]);
+  for (int i = 0; i < HS_PF - 1; i++) prefetch_op(ka.pods + r + i, &s_op[i], r + i < ka.n_ops);
 
   const bool timing = ka.timing != nullptr && gtid == 0;   // diagnostic phase clocks (HS_TIMING=1), block 0 only
   long long tc = timing ? clock64() : 0;
 #define TICK(slot) do { if (timing) { const long long t_ = clock64(); ka.timing[slot] += (unsigned long long)(t_ - tc); tc = t_; } } while (0)
 
   for (; r < ka.n_ops; r++) {
-    const int buf = (r - ka.op_begin) & 1;
-    prefetch_wait();
-    __syncthreads();             // op r is staged; every thread is done with the other buffer and with s_ent
-    if (r + 1 < ka.n_ops) prefetch_op(ka.pods + r + 1, &s_op[buf ^ 1]);
+    const int buf = (r - ka.op_begin) & (HS_PF - 1);
+    prefetch_wait_oldest();
+    __syncthreads();             // op r is staged; every thread is done with op r-1's buffer and with s_ent
+    prefetch_op(ka.pods + r + HS_PF - 1, &s_op[(buf + HS_PF - 1) & (HS_PF - 1)], r + HS_PF - 1 < ka.n_ops);
     const DevPod& pod = s_op[buf];
     if (resident && __any_sync(FULL, dirty || reload)) {   // warp-uniform: refresh what a commit/release changed
       if (reload && gg < ka.n_nodes) load_dev(ka, gg, glane, D);
@@ -322,13 +327,23 @@ hs_decide_kernel(const KernelArgs ka) {
         rows = ka.commit_delta + (size_t)pod.rel_ref * HS_D;
       }
       if (node >= 0 && node < ka.n_nodes && (node % ngroups) == gg) {
-        const int4 delta = rows[glane];
+        int4 delta;
+        if (pod.rel_node >= 0) {          // known pod: the rows came with the op record (no second fetch)
+          const RelDelta rd = reinterpret_cast<const RelDelta*>(&pod.e0)[glane];
+          delta = make_int4((int)rd.slots, rd.mem, (int)rd.cores, 0);
+        } else {
+          delta = rows[glane];
+        }
         if (delta.x | delta.y | delta.z) {
           int4* p = ka.dyn + (size_t)node * HS_D + glane;
-          int4 v = *p;
-          v.x -= delta.x; v.y -= delta.y; v.z -= delta.z;
-          *p = v;
-          if (resident) { D.used -= delta.x; D.mem -= delta.y; D.cores -= delta.z; }
+          if (resident) {                 // the registers are the current copy: store, do not read-modify-write
+            D.used -= delta.x; D.mem -= delta.y; D.cores -= delta.z;
+            *p = make_int4(D.used, D.mem, D.cores, (int)D.dflags);
+          } else {
+            int4 v = *p;
+            v.x -= delta.x; v.y -= delta.y; v.z -= delta.z;
+            *p = v;
+          }
         }
         dirty = true;
         if (!resident) { __syncwarp(gmask); if (glane == 0) refresh_node_score(ka, node); }
@@ -457,6 +472,8 @@ hs_decide_kernel(const KernelArgs ka) {
       slot_arrive(ka.sync + r, bk, s_red);
       if (deferred && __any_sync(FULL, my_key != 0ull))     // warp-uniform: fast_fit is a whole-warp collective
         fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
+      // (choosing the devices here too, in every group that fits, was measured 8 % SLOWER than leaving fast_pick to
+      // the one winner: 5 000 groups pay for it, one benefits)
       win = slot_wait(ka.sync + r, &s_win);
     } else {
       win = slot_argbest(ka, ka.sync + r, barriers, bk, s_red, &s_win);
@@ -494,9 +511,7 @@ hs_decide_kernel(const KernelArgs ka) {
           // ---- commit: each lane of the winning group commits its own device ------------------
           int my_row;
           const int np = fast_pick(glane, (uint32_t)my_node, my_flags, pod, pod.e0, ka, fe, &my_row);
-          uint32_t off = 0;
-          if (glane == 0) off = atomicAdd(ka.counters + 0, (uint32_t)np);
-          off = __shfl_sync(gmask, off, gbase);
+          const uint32_t off = pod.alloc_base;      // rows of this op: a prefix sum the host made, no cursor atomic
           int4 delta = make_int4(0, 0, 0, 0);
           if (my_row >= 0) {
             delta = make_int4(1, fe.memreq, fe.cores, 0);
@@ -505,10 +520,14 @@ hs_decide_kernel(const KernelArgs ka) {
             if (off + (uint32_t)my_row < ka.alloc_cap) ka.allocs[off + my_row] = a;
             if (!dry) {
               int4* p = ka.dyn + (size_t)my_node * HS_D + glane;
-              int4 v = *p;
-              v.x += 1; v.y += fe.memreq; v.z += fe.cores;
-              *p = v;
-              if (resident) { D.used += 1; D.mem += fe.memreq; D.cores += fe.cores; }
+              if (resident) {             // the registers are the current copy: store, do not read-modify-write
+                D.used += 1; D.mem += fe.memreq; D.cores += fe.cores;
+                *p = make_int4(D.used, D.mem, D.cores, (int)D.dflags);
+              } else {
+                int4 v = *p;
+                v.x += 1; v.y += fe.memreq; v.z += fe.cores;
+                *p = v;
+              }
             }
           }
           ka.commit_delta[(size_t)r * HS_D + glane] = delta;
@@ -527,7 +546,7 @@ hs_decide_kernel(const KernelArgs ka) {
         if (glane == 0) {
           int4 delta[HS_D];
           collapse_rows(ent, la, my_nalloc, delta);
-          const uint32_t off = atomicAdd(ka.counters + 0, my_nalloc);
+          const uint32_t off = pod.alloc_base;
           for (uint32_t i = 0; i < my_nalloc && off + i < ka.alloc_cap; i++) ka.allocs[off + i] = la[i];
           if (!dry) {
             store_usage(ka, my_node, delta, +1);

@@ -93,9 +93,14 @@ struct DevPod {             // one op of the stream, 96 B + entries
   int32_t rel_ref;
   int32_t rel_off;          // first of HS_D {slots, mem, cores, 0} int4 rows in the release pool
   int32_t q_idx[2];         // namespace quota rows (KernelArgs.quota) the NVIDIA [0] / MLU [1] Fit consults, -1 = none (quota.go:62-95)
-  uint32_t pad4[6];
+  uint32_t alloc_base;      // FILTER: first DevAlloc row of this op (prefix sum of the ops' worst-case row counts: no cursor atomic)
+  uint32_t pad4[5];
   DevEntry e0;             // the first (usually only) entry rides inside the op record: one 160 B prefetch per op
 };
+// OP_RELEASE of a pod the host knows (rel_node >= 0): the 8 per-device deltas ride in the op record, in the bytes
+// of e0, so the owner needs no second fetch (the rows in rel_pool stay for the streaming and quota paths)
+struct RelDelta { int32_t mem; int16_t cores; uint16_t slots; };
+static_assert(sizeof(RelDelta) * HS_D == 64, "RelDelta rows overlay DevPod::e0");
 static_assert(sizeof(DevEntry) == 64, "DevEntry layout");
 static_assert(sizeof(DevPod) == 160, "DevPod layout: 96 B header + 64 B first entry, 16 B chunks for cp.async");
 
