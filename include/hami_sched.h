@@ -209,8 +209,13 @@ typedef struct hs_ascend_config {
  *                      (:190-195); one registration per configured CommonWord ("BI-V100", "BI-V150", "MR-V100", …)
  *   HS_FIT_COUNT_ONLY  biren (pkg/device/biren/device.go:190-248): health, type, uuid, slots, mutex only; the pick
  *                      records Usedmem 0 and Usedcores = Coresreq as requested (no clamp)
- * PatchAnnotations of both writes EncodePodSingleDevice under the two keys (iluvatar :143-154, biren :167-177).   */
-enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1 };
+ * PatchAnnotations of all three writes EncodePodSingleDevice under the two keys (iluvatar :143-154, biren :167-177,
+ * amd :120-131).
+ *   HS_FIT_AMD        amd (pkg/device/amd/device.go:279-371): health, type (use/no-use type lists, :165-186), uuid,
+ *                      slots, mutex; Memreq <= 0 means the whole card's memory; Coresreq > 0 is a share of the card's
+ *                      cores (Totalcore * Coresreq / 100, clamped to [1, Totalcore]), a whole-memory request without
+ *                      cores takes all cores; the pick records the DEVICE's type string, not k.Type (:341-346)      */
+enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */
@@ -218,6 +223,8 @@ typedef struct hs_vendor_config {
   const char* nouse_uuid_key;
   const char* to_allocate_key;   /* InRequestDevices[word]; NULL = "hami.io/<word>-devices-to-allocate"       */
   const char* allocated_key;     /* SupportDevices[word];   NULL = "hami.io/<word>-devices-allocated"         */
+  const char* use_type_key;      /* HS_FIT_AMD: "amd.com/use-gputype" / "amd.com/nouse-gputype"; NULL = no lists */
+  const char* nouse_type_key;
 } hs_vendor_config;
 
 typedef struct hs_config {

@@ -113,10 +113,11 @@ HS_REQ_NVIDIA, HS_REQ_DCU, HS_REQ_MLU, HS_REQ_ASCEND = 0, 1, 2, 3
 
 class hs_vendor_config(C.Structure):
     _fields_ = [("common_word", C.c_char_p), ("fit_kind", C.c_int32), ("use_uuid_key", C.c_char_p),
-                ("nouse_uuid_key", C.c_char_p), ("to_allocate_key", C.c_char_p), ("allocated_key", C.c_char_p)]
+                ("nouse_uuid_key", C.c_char_p), ("to_allocate_key", C.c_char_p), ("allocated_key", C.c_char_p),
+                ("use_type_key", C.c_char_p), ("nouse_type_key", C.c_char_p)]
 
 
-HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY = 0, 1
+HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD = 0, 1, 2
 
 # The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
 # (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
@@ -126,6 +127,9 @@ DEFAULT_VENDORS = [
     ("MR-V100", HS_FIT_TEMPLATE, None, None, None, None),
     ("MR-V50", HS_FIT_TEMPLATE, None, None, None, None),
     ("Biren", HS_FIT_COUNT_ONLY, "birentech.com/use-gpuuuid", "birentech.com/nouse-gpuuuid", None, None),
+    # amd/device.go:40-52,62-66
+    ("AMD", HS_FIT_AMD, "amd.com/use-gpu-uuid", "amd.com/nouse-gpu-uuid", "hami.io/amd-devices-to-allocate",
+     "hami.io/amd-devices-allocated", "amd.com/use-gputype", "amd.com/nouse-gputype"),
 ]
 
 
@@ -163,8 +167,10 @@ def build_config(node_policy=None, gpu_policy=None, ascend=None, ascend_hami_vnp
     keep = []
     vendors = DEFAULT_VENDORS if vendors is None else vendors
     varr = (hs_vendor_config * max(1, len(vendors)))()
-    for i, (word, kind, use, nouse, toalloc, alloc) in enumerate(vendors):
-        varr[i] = hs_vendor_config(_b(word), kind, _b(use), _b(nouse), _b(toalloc), _b(alloc))
+    for i, v in enumerate(vendors):
+        word, kind, use, nouse, toalloc, alloc = v[:6]
+        use_t, nouse_t = (v[6], v[7]) if len(v) > 6 else (None, None)
+        varr[i] = hs_vendor_config(_b(word), kind, _b(use), _b(nouse), _b(toalloc), _b(alloc), _b(use_t), _b(nouse_t))
     keep.append(varr)
     ascend = DEFAULT_ASCEND if ascend is None else ascend
     arr = (hs_ascend_config * max(1, len(ascend)))()

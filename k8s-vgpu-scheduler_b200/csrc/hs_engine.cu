@@ -137,6 +137,7 @@ struct VendorInfo {
   bool ascend = false, ascend910 = false;
   int gate = 0;             // device-side gate class (HV_*): plain vendors share hygon's gate list (HV_DCU)
   bool count_only = false;  // biren's Fit: no memory / core gates (EF_COUNT_ONLY)
+  bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
 };
 
@@ -623,6 +624,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       const VendorInfo* v = vit == h->vendor_by_word.end() ? nullptr : &h->vendors[vit->second];
       e.vendor = v ? (uint16_t)v->gate : (uint16_t)HV_NONE;
       if (v && v->count_only) e.flags |= EF_COUNT_ONLY;
+      if (v && v->amd) e.flags |= EF_AMD;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
       if (v && v->ascend910) e.flags |= EF_ASCEND910;
@@ -663,7 +665,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     const DevEntry& e = c.entries[0];
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
               !(e.flags & EF_ASCEND910)) ? 1 : 0;
-    if (h->no_fast || (e.flags & EF_COUNT_ONLY)) p.fast = 0;
+    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD))) p.fast = 0;
   }
   quota_rows_for(h, c.meta.ns, p);
   if (p.q_idx[0] >= 0 || p.q_idx[1] >= 0) p.fast = 0;   // the quota check lives in the general evaluator (hs_eval.cuh)
@@ -703,13 +705,17 @@ void apply_host_delta(hs_handle* h, int node, const int4* delta, int sign) {
   h->h_tot[node].y = host_node_score_bits(h, node);
 }
 
-std::string encode_pod_single(const std::vector<std::vector<const hs_alloc_entry*>>& pd) {
-  // EncodePodSingleDevice / EncodeContainerDevices, devices.go:451-484
+std::string encode_pod_single(const std::vector<std::vector<const hs_alloc_entry*>>& pd, const NodeSlot* type_from = nullptr) {
+  // EncodePodSingleDevice / EncodeContainerDevices, devices.go:451-484.  type_from: the vendor's picks carry the
+  // DEVICE's type string instead of k.Type (amd/device.go:341-346)
   std::string res;
   char buf[64];
   for (auto& ctr : pd) {
     for (auto* e : ctr) {
-      res += e->uuid; res += ','; res += e->type_key;
+      const char* type = e->type_key;
+      if (type_from)
+        for (const auto& d : type_from->devs) if (d.uuid == e->uuid) { type = d.type.c_str(); break; }
+      res += e->uuid; res += ','; res += type;
       snprintf(buf, sizeof buf, ",%d,%d:", e->usedmem, e->usedcores);
       res += buf;
     }
@@ -1090,7 +1096,7 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
     for (auto& v : h->vendors) {
       auto it = views.find(v.word);
       if (it == views.end() || it->second.empty()) continue;
-      std::string s = encode_pod_single(it->second);
+      std::string s = encode_pod_single(it->second, v.amd ? &ns : nullptr);
       if (v.word == "MLU") {  // cambricon/device.go:312-332
         annos["CAMBRICON_DSMLU_ASSIGNED"] = "false";
         for (auto& ctr : it->second)
@@ -1389,6 +1395,9 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.ascend910 = false;
       v.gate = HV_DCU;                      // iluvatar's Fit is hygon's gate list (iluvatar/device.go:267-371)
       v.count_only = vc.fit_kind == HS_FIT_COUNT_ONLY;
+      v.amd = vc.fit_kind == HS_FIT_AMD;
+      if (vc.use_type_key) v.use_type = vc.use_type_key;
+      if (vc.nouse_type_key) v.nouse_type = vc.nouse_type_key;
       if (vc.use_uuid_key) v.use_uuid = vc.use_uuid_key;
       if (vc.nouse_uuid_key) v.nouse_uuid = vc.nouse_uuid_key;
       if (vc.to_allocate_key) v.to_allocate = vc.to_allocate_key;

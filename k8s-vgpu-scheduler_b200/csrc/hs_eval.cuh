@@ -139,6 +139,7 @@ __device__ __forceinline__ uint32_t uuid_mask_lookup(const uint32_t* pool, uint3
 struct FitCtx {
   int tmp_dev[HS_D];    // tmpDevs[k.Type]: device slots in pick order
   int tmp_mem[HS_D];    // their resolved memreq
+  int tmp_cores[HS_D];  // EF_AMD only: the per-device core share (every other vendor records `cores` for all picks)
   int ntmp;
   int cores;            // k.Coresreq after the 100 clamp
 };
@@ -283,6 +284,30 @@ __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e,
         k_nums--;
         fc.tmp_dev[fc.ntmp] = d;
         fc.tmp_mem[fc.ntmp] = 0;
+        fc.ntmp++;
+      }
+      if (k_nums == 0) return true;
+      continue;
+    }
+    if (e.flags & EF_AMD) {               // amd/device.go:308-350
+      int memReq = e.memreq;
+      if (memReq <= 0 && w.totmem[d] > 0) memReq = w.totmem[d];
+      if (w.totmem[d] - w.mem[d] < memReq) { REASON(4); continue; }
+      int coreReq = 0;
+      if (e.coresreq > 0) {
+        if (w.totcore[d] <= 0) { REASON(5); continue; }
+        coreReq = (int)((unsigned)w.totcore[d] * (unsigned)e.coresreq) / 100;
+        coreReq = coreReq < 1 ? 1 : coreReq;
+        coreReq = coreReq > w.totcore[d] ? w.totcore[d] : coreReq;
+      } else if (w.totmem[d] > 0 && memReq >= w.totmem[d]) {
+        coreReq = w.totcore[d];
+      }
+      if (w.totcore[d] - w.cores[d] < coreReq) { REASON(5); continue; }
+      if (k_nums > 0) {
+        k_nums--;
+        fc.tmp_dev[fc.ntmp] = d;
+        fc.tmp_mem[fc.ntmp] = memReq;
+        fc.tmp_cores[fc.ntmp] = coreReq;
         fc.ntmp++;
       }
       if (k_nums == 0) return true;
@@ -468,14 +493,15 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
     bool missing_net = false;
     for (int t = 0; t < fc.ntmp; t++) {
       const int d = fc.tmp_dev[t];
+      const int pick_cores = (e.flags & EF_AMD) ? fc.tmp_cores[t] : fc.cores;
       w.used[d] += 1;
-      w.cores[d] += fc.cores;
+      w.cores[d] += pick_cores;
       w.mem[d] += fc.tmp_mem[t];
       if (MODE == EV_RECORD && out.n_alloc < HS_MAX_ALLOC) {
         DevAlloc a;
         a.entry = (uint8_t)(ei);
         a.dev = (uint8_t)d;
-        a.usedcores = (int16_t)fc.cores;
+        a.usedcores = (int16_t)pick_cores;
         a.usedmem = fc.tmp_mem[t];
         out.allocs[out.n_alloc++] = a;
       }

@@ -362,7 +362,8 @@ namespace {
 
 // PLAIN: iluvatar's Fit (iluvatar/device.go:267-371) = the hygon gate list with checkType "key equals the word";
 // COUNT_ONLY: biren's Fit (biren/device.go:190-248) = the gates up to mutex, Usedmem 0, Usedcores as requested
-enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY };
+// AMD: amd/device.go:279-371 — type lists like hygon, whole-card memory by default, cores as a share of the card
+enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY, AMD };
 
 struct FitGates {
   Vendor vendor;
@@ -556,6 +557,7 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
           break;
         }
         case Vendor::DCU:
+        case Vendor::AMD:          // checkAMDType, amd/device.go:165-186: the same two lists
           found = CheckType(pod.Annotations, dev->Type, g.useType, g.noUseType);
           break;
         case Vendor::MLU:
@@ -583,6 +585,30 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
         k.Nums--;
         ContainerDevice cd;
         cd.Idx = (int)dev->Index; cd.UUID = dev->ID; cd.Type = k.Type; cd.Usedmem = 0; cd.Usedcores = k.Coresreq;
+        tmpDevs.push_back(cd);
+      }
+      if (k.Nums == 0) { FitResult r; r.fit = true; r.devs = tmpDevs; return r; }
+      continue;
+    }
+    if (g.vendor == Vendor::AMD) {          // amd/device.go:308-350: whole card by default, cores as a share of the card
+      int32_t memReq = k.Memreq;
+      if (memReq <= 0 && dev->Totalmem > 0) memReq = dev->Totalmem;
+      if (i32sub(dev->Totalmem, dev->Usedmem) < memReq) { reason["CardInsufficientMemory"]++; continue; }
+      int32_t coreReq = 0;
+      if (k.Coresreq > 0) {
+        if (dev->Totalcore <= 0) { reason["CardInsufficientCore"]++; continue; }
+        coreReq = i32mul(dev->Totalcore, k.Coresreq) / 100;
+        coreReq = std::max(coreReq, (int32_t)1);
+        coreReq = std::min(coreReq, dev->Totalcore);
+      } else if (dev->Totalmem > 0 && memReq >= dev->Totalmem) {
+        coreReq = dev->Totalcore;
+      }
+      if (i32sub(dev->Totalcore, dev->Usedcores) < coreReq) { reason["CardInsufficientCore"]++; continue; }
+      if (k.Nums > 0) {
+        k.Nums--;
+        ContainerDevice cd;
+        cd.Idx = (int)dev->Index; cd.UUID = dev->ID; cd.Type = dev->Type;   // the registered product type, not k.Type (:341-346)
+        cd.Usedmem = memReq; cd.Usedcores = coreReq;
         tmpDevs.push_back(cd);
       }
       if (k.Nums == 0) { FitResult r; r.fit = true; r.devs = tmpDevs; return r; }
@@ -690,7 +716,8 @@ class PlainDevices : public Devices {
   FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
                 const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
                 const QuotaManager* quota) const override {
-    FitGates g{v_.FitKind == 1 ? Vendor::COUNT_ONLY : Vendor::PLAIN, v_.CommonWord, "", "", v_.UseUUID, v_.NoUseUUID};
+    FitGates g{v_.FitKind == 1 ? Vendor::COUNT_ONLY : (v_.FitKind == 2 ? Vendor::AMD : Vendor::PLAIN), v_.CommonWord,
+               v_.UseType, v_.NoUseType, v_.UseUUID, v_.NoUseUUID};
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
   void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {

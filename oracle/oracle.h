@@ -193,7 +193,7 @@ struct Config {
   std::vector<AscendConfig> Ascend;
   bool AscendHamiVnpuCore = false;
   // vendors with a plain Fit (hs_vendor_config): iluvatar's CommonWords, biren
-  struct PlainVendor { std::string CommonWord; int FitKind = 0; std::string UseUUID, NoUseUUID, ToAllocate, Allocated; };
+  struct PlainVendor { std::string CommonWord; int FitKind = 0; std::string UseUUID, NoUseUUID, ToAllocate, Allocated, UseType, NoUseType; };
   std::vector<PlainVendor> Plain;
 };
 

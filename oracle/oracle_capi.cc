@@ -141,6 +141,8 @@ oracle_handle* oracle_create(const hs_config* cfg) {
       pv.NoUseUUID = v.nouse_uuid_key ? v.nouse_uuid_key : "hami.io/no-use-" + pv.CommonWord + "-uuid";
       pv.ToAllocate = v.to_allocate_key ? v.to_allocate_key : "hami.io/" + pv.CommonWord + "-devices-to-allocate";
       pv.Allocated = v.allocated_key ? v.allocated_key : "hami.io/" + pv.CommonWord + "-devices-allocated";
+      pv.UseType = str(v.use_type_key);
+      pv.NoUseType = str(v.nouse_type_key);
       c.Plain.push_back(pv);
     }
   auto* o = new oracle_handle();

@@ -58,12 +58,48 @@ def test_biren_fit(orc, case):
     assert reason == case["wantReason"]
 
 
+AMD_CASES = json.load(open(os.path.join(ROOT, "tests", "golden", "ingest_funcs.json")))["amd_fit"]
+
+
+@pytest.mark.parametrize("case", AMD_CASES, ids=[c["name"][:40] for c in AMD_CASES])
+def test_amd_fit(orc, case):
+    # amd/device_test.go:300-478 (TestDevices_Fit, t.Run blocks extracted by tools/extract_golden_ingest.py)
+    fit, got, reason = run_fit(orc, "AMD", case["devices"], case["request"], case["annos"] or {})
+    assert fit == case["wantFit"]
+    if case["wantUUIDs"]:
+        assert [g[0] for g in got] == case["wantUUIDs"]
+    if "wantLen" in case:
+        assert len(got) == case["wantLen"]
+    if "wantUsedmem" in case:
+        assert got[0][2] == case["wantUsedmem"]
+    if "wantUsedcores" in case:
+        assert got[0][3] == case["wantUsedcores"]
+    if "wantReason" in case:
+        assert reason == case["wantReason"]
+    if "wantReasonContains" in case:
+        assert case["wantReasonContains"] in reason
+
+
+def test_amd_allocation_keeps_the_product_type():
+    # amd/device_test.go:354-370: the annotation names the registered product type, the PodDevices key stays "AMD"
+    o = oa.Oracle("binpack", "spread")
+    o.node_upsert({"name": "amd-0", "devices": [{"id": "dev-0", "index": 0, "count": 2, "devmem": 1000, "devcore": 100,
+                                                 "type": "AMD_Instinct_MI300X_VF", "numa": 0, "mode": "", "health": True, "vendor": "AMD"}]})
+    r = o.filter({"uid": "p", "ns": "default", "name": "p", "annotations": {}, "n_init": 0,
+                  "containers": [[{"key": "AMD", "type": "AMD", "nums": 1, "memreq": 100, "mempct": 0, "coresreq": 10}]]})
+    o.close()
+    assert r["status"] == abi.HS_FIT
+    assert r["annotations"]["hami.io/amd-devices-allocated"] == "dev-0,AMD_Instinct_MI300X_VF,100,10:;"
+    assert [d[0] for d in r["devices"]["AMD"][0]] == ["dev-0"]
+    assert r["devices"].get("AMD_Instinct_MI300X_VF") == [[]]        # base-type padding (score.go:278-282), no devices under it
+
+
 # ---- GPU parity on a generated cluster ---------------------------------------------------------------------
 def _cluster(n_nodes, n_pods, seed=11):
     rng = random.Random(seed)
     nodes, kinds = [], []
     for i in range(n_nodes):
-        kind = ("NVIDIA", "MR-V100", "BI-V150", "Biren")[i % 4]
+        kind = ("NVIDIA", "MR-V100", "BI-V150", "Biren", "AMD")[i % 5]
         nd = rng.randrange(2, 9)
         devs = []
         for d in range(nd):
@@ -73,6 +109,10 @@ def _cluster(n_nodes, n_pods, seed=11):
             elif kind == "Biren":
                 devs.append({"id": "BR-%03d-%d" % (i, d), "index": d, "count": rng.choice([1, 1, 2]), "devmem": 0, "devcore": 0,
                              "type": "Biren", "numa": 0, "mode": "", "health": rng.random() > 0.05, "vendor": "Biren"})
+            elif kind == "AMD":
+                devs.append({"id": "AMD-%03d-%d" % (i, d), "index": d, "count": 4, "devmem": 196608, "devcore": rng.choice([64, 100, 304]),
+                             "type": rng.choice(["AMD_Instinct_MI300X_VF", "AMD_Instinct_MI250"]), "numa": 0, "mode": "",
+                             "health": rng.random() > 0.05, "vendor": "AMD"})
             else:
                 devs.append({"id": "ILU-%03d-%d" % (i, d), "index": d, "count": 4, "devmem": 32768, "devcore": 100,
                              "type": kind, "numa": 0, "mode": "", "health": rng.random() > 0.05, "vendor": kind})
@@ -80,7 +120,7 @@ def _cluster(n_nodes, n_pods, seed=11):
         kinds.append(kind)
     ops, live = [], []
     for p in range(n_pods):
-        kind = rng.choice(["NVIDIA", "MR-V100", "BI-V150", "Biren", "Biren", "MR-V50"])   # MR-V50: registered, no node has it
+        kind = rng.choice(["NVIDIA", "MR-V100", "BI-V150", "Biren", "Biren", "AMD", "AMD", "MR-V50"])   # MR-V50: registered, no node has it
         annos = {}
         if rng.random() < 0.3:
             annos["hami.io/gpu-scheduler-policy"] = rng.choice(["binpack", "spread", "mutex"])
@@ -92,6 +132,15 @@ def _cluster(n_nodes, n_pods, seed=11):
             if rng.random() < 0.15:
                 n = rng.choice([x for x, k in zip(nodes, kinds) if k == "Biren"])
                 annos[rng.choice(["birentech.com/use-gpuuuid", "birentech.com/nouse-gpuuuid"])] = n["devices"][0]["id"]
+        elif kind == "AMD":
+            req = {"key": kind, "type": kind, "nums": rng.choice([1, 1, 2, 4]), "memreq": rng.choice([0, 0, 65536, 98304]), "mempct": 0,
+                   "coresreq": rng.choice([0, 1, 25, 50, 101])}
+            r = rng.random()
+            if r < 0.15:
+                annos[rng.choice(["amd.com/use-gputype", "amd.com/nouse-gputype"])] = rng.choice(["MI300X", "mi250, MI210", "Instinct"])
+            elif r < 0.25:
+                n = rng.choice([x for x, k in zip(nodes, kinds) if k == "AMD"])
+                annos[rng.choice(["amd.com/use-gpu-uuid", "amd.com/nouse-gpu-uuid"])] = n["devices"][0]["id"]
         else:
             req = {"key": kind, "type": kind, "nums": rng.choice([1, 1, 2, 4]), "memreq": rng.choice([0, 4096, 16384]),
                    "mempct": rng.choice([101, 101, 50]), "coresreq": rng.choice([0, 30, 100])}
@@ -123,5 +172,8 @@ def test_plain_vendors_gpu_parity():
             k = arg["containers"][0][0]["type"]
             fits[k] = fits.get(k, 0) + 1
     assert fits.get("Biren", 0) > 20 and fits.get("MR-V100", 0) > 20 and fits.get("BI-V150", 0) > 20 and "MR-V50" not in fits
+    assert fits.get("AMD", 0) > 20
+    amd = next(r for (kind, arg), r in zip(ops, ref) if kind == "filter" and r["status"] == abi.HS_FIT and arg["containers"][0][0]["type"] == "AMD")
+    assert ",AMD_Instinct_" in amd["annotations"]["hami.io/amd-devices-allocated"]      # the device's type, not the key
     sample = next(r for (kind, arg), r in zip(ops, ref) if kind == "filter" and r["status"] == abi.HS_FIT and arg["containers"][0][0]["type"] == "Biren")
     assert "hami.io/Biren-devices-allocated" in sample["annotations"] and "hami.io/Biren-devices-to-allocate" in sample["annotations"]

@@ -62,10 +62,53 @@ def pair_score_cases(ref):
     return out
 
 
+def amd_fit_cases(ref):
+    """pkg/device/amd/device_test.go TestDevices_Fit is a list of t.Run blocks, not a table."""
+    rel = "pkg/device/amd/device_test.go"
+    src = open(os.path.join(ref, rel)).read()
+    body = X.find_func(src, "TestDevices_Fit")
+    base = src[:src.index(body)].count("\n") + 1
+    X.IDENTS.update({"AMDDevice": "AMD", "AMDUseUUID": "amd.com/use-gpu-uuid", "AMDNoUseUUID": "amd.com/nouse-gpu-uuid",
+                     "AMDInUse": "amd.com/use-gputype", "AMDNoUse": "amd.com/nouse-gputype"})
+    out = []
+    starts = [m.start() for m in re.finditer(r'\bt\.Run\("', body)] + [len(body)]
+    for a, b in zip(starts, starts[1:]):
+        blk = body[a:b]
+        name = re.match(r't\.Run\("((?:[^"\\]|\\.)*)"', blk).group(1)
+        mp = re.search(r'productType :?= "([^"]*)"', blk)
+        if mp:
+            X.IDENTS["productType"] = mp.group(1)
+
+        def lit(pattern):
+            m = re.search(pattern, blk)
+            return X.simplify(X.P(X.tokenize(blk[m.end():])).parse_expr()) if m else None
+        case = {"name": name, "source": "%s:%d" % (rel, base + body[:a].count("\n")),
+                "devices": lit(r"devices := "), "request": lit(r"req := "), "annos": lit(r"Annotations:\s*") or {}}
+        case["wantFit"] = re.search(r"assert\.Equal\(t, (true|false), ok\)", blk).group(1) == "true"
+        case["wantUUIDs"] = [u for _, u in sorted((int(i), u) for u, i in re.findall(r'assert\.Equal\(t, "([^"]+)", got\[AMDDevice\]\[(\d+)\]\.UUID\)', blk))]
+        for field in ("Usedmem", "Usedcores"):
+            m = re.search(r"assert\.Equal\(t, int32\((\d+)\), got\[AMDDevice\]\[0\]\.%s\)" % field, blk)
+            if m:
+                case["want" + field] = int(m.group(1))
+        if re.search(r"assert\.Equal\(t, productType, got\[AMDDevice\]\[0\]\.Type\)", blk):
+            case["wantType"] = X.IDENTS["productType"]
+        m = re.search(r"strings\.Contains\(reason, common\.(\w+)\)", blk)
+        if m:
+            case["wantReasonContains"] = X.IDENTS["common." + m.group(1)]
+        elif re.search(r'assert\.Equal\(t, "", reason\)', blk):
+            case["wantReason"] = ""
+        m = re.search(r"assert\.Equal\(t, (\d+), len\(got\[AMDDevice\]\)\)", blk)
+        if m:
+            case["wantLen"] = int(m.group(1))
+        out.append(case)
+    return out
+
+
 def main():
     ref = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
     doc = {"note": "extracted from the reference's own tests by tools/extract_golden_ingest.py",
-           "init_container": init_container_cases(ref), "nvidia_get_node_devices": pair_score_cases(ref)}
+           "init_container": init_container_cases(ref), "nvidia_get_node_devices": pair_score_cases(ref),
+           "amd_fit": amd_fit_cases(ref)}
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "ingest_funcs.json")
     with open(path, "w") as f:
         json.dump(doc, f, indent=1, sort_keys=True)
