@@ -269,6 +269,8 @@ struct hs_handle {
   }
   int32_t mem_factor[16] = {1, 1, 256, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};   // ResourceNames.MemoryFactor; MLU = 256 (cambricon/device.go:60)
   bool any_quota_limit = false;
+  NsQuota* last_quota = nullptr;
+  std::string last_quota_ns;
   std::vector<std::pair<std::string, int>> quota_rows;           // rows of the current batch's device table
   DBuf<long long> b_quota;
   hs_handle* sim = nullptr;             // child handle holding the transient inventory of hs_filter_simulate
@@ -528,8 +530,10 @@ void quota_track(hs_handle* h, const std::string& ns, int node, const int4* delt
   for (int v = 0; v < 16; v++) {
     if (!any[v]) continue;
     if (!nq) {
-      if (sign > 0) nq = &h->quota[ns];
+      if (h->last_quota && h->last_quota_ns == ns) nq = h->last_quota;          // streams are mostly one namespace
+      else if (sign > 0) nq = &h->quota[ns];
       else { auto it = h->quota.find(ns); if (it == h->quota.end()) return; nq = &it->second; }
+      h->last_quota = nq; h->last_quota_ns = ns;                                  // unordered_map nodes do not move
     }
     hs_handle::QuotaEnt& q = nq->v[v];
     if (sign > 0) {
@@ -1497,6 +1501,25 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
     vec.erase(std::remove(vec.begin(), vec.end(), ((uint32_t)slot << 8) | (uint32_t)d), vec.end());
     if (vec.empty()) h->uuid_index.erase(ns.devs[d].uuid);
   }
+  {   // the pods of this node remember their devices by slot: follow the devices to their new slots (a vanished UUID
+      // takes its share of the usage with it, exactly like the join by UUID in the reference)
+    int new_of[HS_D];
+    bool identity = true;
+    for (size_t d = 0; d < ns.devs.size() && d < (size_t)HS_D; d++) {
+      new_of[d] = -1;
+      for (size_t k = 0; k < sorted.size(); k++) if (sorted[k].uuid == ns.devs[d].uuid) { new_of[d] = (int)k; break; }
+      if (new_of[d] != (int)d) identity = false;
+    }
+    if (!identity)
+      for (auto& kv : h->pods) {
+        if (kv.second.node != slot) continue;
+        int4 moved[HS_D];
+        for (int k = 0; k < HS_D; k++) moved[k] = make_int4(0, 0, 0, 0);
+        for (size_t d = 0; d < ns.devs.size() && d < (size_t)HS_D; d++)
+          if (new_of[d] >= 0) moved[new_of[d]] = kv.second.delta[d];
+        for (int k = 0; k < HS_D; k++) kv.second.delta[k] = moved[k];
+      }
+  }
   if (!ns.alive) { h->n_alive++; }
   ns.alive = true;
   ns.devs = sorted;
@@ -1563,13 +1586,14 @@ int32_t hs_node_remove(hs_handle* h, const char* name) {
     vec.erase(std::remove(vec.begin(), vec.end(), ((uint32_t)slot << 8) | (uint32_t)d), vec.end());
     if (vec.empty()) h->uuid_index.erase(ns.devs[d].uuid);
   }
+  // rmNodeDevices drops the node from the candidate set only: the pods bound to it stay in podManager, keep being
+  // released against it, and count again when the node returns with the same UUIDs (getNodesUsage joins pods and nodes
+  // by UUID, scheduler.go:773-785).  So the devices and their usage stay; only liveness goes.
   ns.alive = false;
-  ns.devs.clear();
   h->n_alive--;
   h->has_dead = true;
-  h->h_flags[slot] = 0;
-  h->h_tot[slot] = make_int4(0, 0, 0, 0);
-  for (int d = 0; d < HS_D; d++) { h->h_dyn[inv_idx(slot, d)] = make_int4(0, 0, 0, 0); h->h_stat[inv_idx(slot, d)] = make_int4(0, 0, 0, 0); }
+  h->h_flags[slot] &= ~NF_ALIVE;
+  h->h_tot[slot].x = (int)h->h_flags[slot];
   mark_dirty(h, slot);
   return HS_OK;
 }
