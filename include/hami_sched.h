@@ -215,7 +215,12 @@ typedef struct hs_ascend_config {
  *                      slots, mutex; Memreq <= 0 means the whole card's memory; Coresreq > 0 is a share of the card's
  *                      cores (Totalcore * Coresreq / 100, clamped to [1, Totalcore]), a whole-memory request without
  *                      cores takes all cores; the pick records the DEVICE's type string, not k.Type (:341-346)      */
-enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2 };
+enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
+       /* mthreads (pkg/device/mthreads/device.go:289-405): the template gates plus customFilterRule (:266-276) — every
+        * device an earlier container of the pod received must be the candidate itself, reason
+        * "CardNotFoundCustomFilterRule"; PatchAnnotations (:155-177) writes only the allocated key plus
+        * mthreads.com/gpu-index, mthreads.com/predicate-node and mthreads.com/predicate-time (returned empty)         */
+       HS_FIT_MTHREADS = 3 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */

@@ -117,7 +117,7 @@ class hs_vendor_config(C.Structure):
                 ("use_type_key", C.c_char_p), ("nouse_type_key", C.c_char_p)]
 
 
-HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD = 0, 1, 2
+HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS = 0, 1, 2, 3
 
 # The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
 # (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
@@ -130,6 +130,9 @@ DEFAULT_VENDORS = [
     # amd/device.go:40-52,62-66
     ("AMD", HS_FIT_AMD, "amd.com/use-gpu-uuid", "amd.com/nouse-gpu-uuid", "hami.io/amd-devices-to-allocate",
      "hami.io/amd-devices-allocated", "amd.com/use-gputype", "amd.com/nouse-gputype"),
+    # mthreads/device.go:44-58,76-80
+    ("Mthreads", HS_FIT_MTHREADS, "mthreads.ai/use-gpuuuid", "mthreads.ai/nouse-gpuuuid",
+     "hami.io/mthreads-vgpu-devices-to-allocate", "hami.io/mthreads-vgpu-devices-allocated"),
 ]
 
 

@@ -137,6 +137,7 @@ struct VendorInfo {
   bool ascend = false, ascend910 = false;
   int gate = 0;             // device-side gate class (HV_*): plain vendors share hygon's gate list (HV_DCU)
   bool count_only = false;  // biren's Fit: no memory / core gates (EF_COUNT_ONLY)
+  bool mthreads = false;    // mthreads' Fit: template gates + customFilterRule; its own annotation set (EF_MTHREADS)
   bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
 };
@@ -256,7 +257,7 @@ struct hs_handle {
   // device.QuotaManager (quota.go): (namespace, vendor id) -> {memory, cores}; Used is tracked for every namespace
   // (addUsageLocked auto-creates entries), rows with a limit set travel to the device with each batch
   struct QuotaEnt { int64_t limit[2] = {0, 0}; bool set[2] = {false, false}; int64_t used[2] = {0, 0}; };
-  struct NsQuota { QuotaEnt v[16]; uint32_t present = 0; };      // per namespace: one entry per vendor id, `present` = entry exists
+  struct NsQuota { QuotaEnt v[32]; uint32_t present = 0; };      // per namespace: one entry per vendor id, `present` = entry exists
   std::unordered_map<std::string, NsQuota> quota;
   QuotaEnt* quota_find(const std::string& ns, int vid) {
     auto it = quota.find(ns);
@@ -267,7 +268,7 @@ struct hs_handle {
     q.present |= 1u << vid;
     return q.v[vid];
   }
-  int32_t mem_factor[16] = {1, 1, 256, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};   // ResourceNames.MemoryFactor; MLU = 256 (cambricon/device.go:60)
+  int32_t mem_factor[32] = {1, 1, 256, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};   // ResourceNames.MemoryFactor; MLU = 256 (cambricon/device.go:60)
   bool any_quota_limit = false;
   NsQuota* last_quota = nullptr;
   std::string last_quota_ns;
@@ -519,15 +520,15 @@ void quota_rows_for(hs_handle* h, const std::string& ns, DevPod& p) {
 // countPodDevices + addUsageLocked / rmUsageLocked (quota.go:97-184) on the host mirror, all vendors
 void quota_track(hs_handle* h, const std::string& ns, int node, const int4* delta, int sign) {
   const NodeSlot& nsl = h->nodes[node];
-  int64_t mem[16] = {0}, core[16] = {0};
-  bool any[16] = {false};
+  int64_t mem[32] = {0}, core[32] = {0};
+  bool any[32] = {false};
   for (size_t d = 0; d < nsl.devs.size() && d < (size_t)HS_D; d++) {
     if (!(delta[d].x | delta[d].y | delta[d].z)) continue;
-    const int v = nsl.devs[d].vendor_id & 15;
+    const int v = nsl.devs[d].vendor_id & 31;
     mem[v] += delta[d].y; core[v] += delta[d].z; any[v] = true;
   }
   hs_handle::NsQuota* nq = nullptr;
-  for (int v = 0; v < 16; v++) {
+  for (int v = 0; v < 32; v++) {
     if (!any[v]) continue;
     if (!nq) {
       if (h->last_quota && h->last_quota_ns == ns) nq = h->last_quota;          // streams are mostly one namespace
@@ -629,6 +630,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       e.vendor = v ? (uint16_t)v->gate : (uint16_t)HV_NONE;
       if (v && v->count_only) e.flags |= EF_COUNT_ONLY;
       if (v && v->amd) e.flags |= EF_AMD;
+      if (v && v->mthreads) e.flags |= EF_MTHREADS;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
       if (v && v->ascend910) e.flags |= EF_ASCEND910;
@@ -669,7 +671,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     const DevEntry& e = c.entries[0];
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
               !(e.flags & EF_ASCEND910)) ? 1 : 0;
-    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD))) p.fast = 0;
+    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS))) p.fast = 0;
   }
   quota_rows_for(h, c.meta.ns, p);
   if (p.q_idx[0] >= 0 || p.q_idx[1] >= 0) p.fast = 0;   // the quota check lives in the general evaluator (hs_eval.cuh)
@@ -1111,6 +1113,18 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
             break;
           }
       }
+      if (v.mthreads) {   // mthreads/device.go:155-177: allocated key only, card indices of the last container with devices
+        annos[v.allocated] = s;
+        for (auto& ctr : it->second) {
+          if (ctr.empty()) continue;
+          std::string value;
+          for (auto* e : ctr) { if (!value.empty()) value += ","; value += std::to_string(e->idx); }
+          annos["mthreads.com/gpu-index"] = value;
+          annos["mthreads.com/predicate-time"] = "";
+          annos["mthreads.com/predicate-node"] = ns.name;
+        }
+        continue;
+      }
       annos[v.to_allocate] = s;
       annos[v.allocated] = s;
       if (v.ascend) {  // ascend/device.go:221-253
@@ -1331,7 +1345,7 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
     if (!h->b_quota.ensure(h->quota_rows.size() * 4)) { h->err = "out of memory for the quota table"; return HS_ERR_CUDA; }
     for (size_t i = 0; i < h->quota_rows.size(); i++) {
       const hs_handle::QuotaEnt& q = h->quota_at(h->quota_rows[i].first, h->quota_rows[i].second);
-      const int32_t f = h->mem_factor[h->quota_rows[i].second & 15];
+      const int32_t f = h->mem_factor[h->quota_rows[i].second & 31];
       h->b_quota.h[i * 4 + 0] = q.set[0] ? (f > 1 ? q.limit[0] * (int64_t)f : q.limit[0]) : INT64_MAX;   // quota.go:80-84
       h->b_quota.h[i * 4 + 1] = q.used[0];
       h->b_quota.h[i * 4 + 2] = q.set[1] ? q.limit[1] : INT64_MAX;
@@ -1382,7 +1396,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   add_vendor(h, "DCU", false);
   add_vendor(h, "MLU", false);
   if (cfg)
-    for (uint32_t i = 0; i < cfg->n_ascend && h->vendors.size() < 15; i++) {
+    for (uint32_t i = 0; i < cfg->n_ascend && h->vendors.size() < 31; i++) {
       add_vendor(h, cfg->ascend[i].common_word ? cfg->ascend[i].common_word : "", true);
       VendorInfo& v = h->vendors.back();
       for (uint32_t t = 0; t < cfg->ascend[i].n_templates; t++)
@@ -1391,7 +1405,7 @@ hs_handle* hs_create(const hs_config* cfg) {
                        [](const std::pair<std::string, int64_t>& a, const std::pair<std::string, int64_t>& b) { return a.second < b.second; });
     }
   if (cfg)
-    for (uint32_t i = 0; i < cfg->n_vendors && h->vendors.size() < 15; i++) {
+    for (uint32_t i = 0; i < cfg->n_vendors && h->vendors.size() < 31; i++) {
       const hs_vendor_config& vc = cfg->vendors[i];
       if (!vc.common_word || h->vendor_by_word.count(vc.common_word)) continue;
       add_vendor(h, vc.common_word, false);
@@ -1400,6 +1414,7 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.gate = HV_DCU;                      // iluvatar's Fit is hygon's gate list (iluvatar/device.go:267-371)
       v.count_only = vc.fit_kind == HS_FIT_COUNT_ONLY;
       v.amd = vc.fit_kind == HS_FIT_AMD;
+      v.mthreads = vc.fit_kind == HS_FIT_MTHREADS;
       if (vc.use_type_key) v.use_type = vc.use_type_key;
       if (vc.nouse_type_key) v.nouse_type = vc.nouse_type_key;
       if (vc.use_uuid_key) v.use_uuid = vc.use_uuid_key;
@@ -1715,7 +1730,7 @@ int32_t hs_quota_memory_factor(hs_handle* h, const char* vendor, int32_t factor)
   if (!h) return HS_ERR_INVALID;
   const int vid = quota_vendor(h, vendor);
   if (vid < 0 || factor < 1) return HS_ERR_INVALID;
-  h->mem_factor[vid & 15] = factor;
+  h->mem_factor[vid & 31] = factor;
   return HS_OK;
 }
 

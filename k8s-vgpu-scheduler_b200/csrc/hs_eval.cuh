@@ -18,6 +18,7 @@ struct NodeWork {
   uint32_t packed[HS_D], dflags[HS_D];
   float score[HS_D];                                 // DeviceListsScore.Score
   uint32_t order;                                    // nibble i = device slot at list position i
+  uint32_t mth_prev;                                 // EF_MTHREADS: device slots the pod's earlier containers (of this phase) received
   int ndev;
 };
 
@@ -323,6 +324,8 @@ __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e,
     if (etc - w.cores[d] < fc.cores) { REASON(5); continue; }
     if (etc == 100 && fc.cores == 100 && w.used[d] > 0) { REASON(9); continue; }
     if (etc != 0 && w.cores[d] == etc && fc.cores == 0) { REASON(3); continue; }
+    // customFilterRule, mthreads/device.go:266-276,362-366: the pod's earlier containers all sit on this very card
+    if ((e.flags & EF_MTHREADS) && (w.mth_prev & ~(1u << d))) { REASON(10); continue; }
     if (k_nums > 0) {
       if (decrement) k_nums--;
       fc.tmp_dev[fc.ntmp] = d;
@@ -489,6 +492,8 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
     if (qa && (e.vendor == HV_NVIDIA || e.vendor == HV_MLU))
       quota_append(*qa, e.vendor == HV_NVIDIA ? 0 : 1, fc.tmp_dev, fc.tmp_mem, fc.ntmp, fc.cores);
     // AddResourceUsage per pick (nvidia/device.go:645-664 non-MIG; identical for the other vendors)
+    if (e.flags & EF_MTHREADS)
+      for (int t = 0; t < fc.ntmp; t++) w.mth_prev |= 1u << fc.tmp_dev[t];   // devinput[k.Type] grows by this container (score.go:132)
     int netcnt_max = 0;
     bool missing_net = false;
     for (int t = 0; t < fc.ntmp; t++) {
@@ -537,6 +542,7 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   QuotaAcc* qa = nullptr;
   if (ka.quota != nullptr && (pod.q_idx[0] >= 0 || pod.q_idx[1] >= 0)) { quota_load(qacc, pod, ka); qa = &qacc; }
   const bool base_key[2] = {(nflags & NF_BASE_NV) != 0, (nflags & NF_BASE_MLU) != 0};
+  w.mth_prev = 0;
 
   if (pod.n_init > 0) {
     int bu[HS_D], bm[HS_D], bc[HS_D];
@@ -554,6 +560,7 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
     }
   }
   w.order = identity;
+  w.mth_prev = 0;
   if (qa) quota_reset_lists(*qa);     // score.Devices starts empty for the app containers (score.go:321-326)
   int app_index = 0;
   for (int c = pod.n_init; c < pod.n_ctr; c++) {

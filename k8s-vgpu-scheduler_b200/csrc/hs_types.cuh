@@ -28,7 +28,7 @@
 #define PK_NUMA(x) ((int)((x) & 255u))
 #define PK_TYPE(x) (((x) >> 8) & 63u)
 #define PK_INDEX(x) ((int)(((x) >> 14) & 255u))
-#define PK_VENDOR(x) (((x) >> 22) & 15u)
+#define PK_VENDOR(x) (((x) >> 22) & 31u)
 
 // node_flags: bits0-3 ndev | bit4 alive | bit5 pair scores uniform | bit6 hami-vnpu-core supported
 #define NF_NDEV(x) ((int)((x) & 15u))
@@ -39,7 +39,7 @@
 #define NF_BASE_MLU 256u    // … Type == "MLU"
 
 // vendor predicate ids (device-side switch, one code path, no dispatch layer)
-enum { HV_NVIDIA = 0, HV_DCU = 1, HV_MLU = 2, HV_ASCEND0 = 3, HV_NONE = 15 };
+enum { HV_NVIDIA = 0, HV_DCU = 1, HV_MLU = 2, HV_ASCEND0 = 3, HV_NONE = 31 };   // 5-bit ids: up to 31 registered vendors
 
 // GPU-policy comparator (policy/gpu_policy.go:77-167), resolved on the host
 enum { SORT_BINPACK = 0, SORT_SPREAD = 1, SORT_MUTEX = 2, SORT_NUMA_BINPACK = 3, SORT_NUMA_SPREAD = 4, SORT_CHAIN = 5 };
@@ -49,7 +49,8 @@ enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
 #define EF_ASCEND910 1u     // CommonWord has prefix "Ascend910": NetworkID topology + ScoreNode
 #define EF_ASCEND910C 2u    // k.Type == "Ascend910C": module pairing
 #define EF_MIGMODE_OK 4u    // pod's vgpu-mode annotation is absent or contains "mig" (isMIGRequest)
-#define EF_AMD 16u          // amd's Fit (amd/device.go:279-371): whole-card memory by default, cores as a share of the card
+#define EF_MTHREADS 32u     // mthreads' Fit (mthreads/device.go:289-405): template gates + customFilterRule (one card per pod)
+#define EF_AMD 16u         // amd's Fit (amd/device.go:279-371): whole-card memory by default, cores as a share of the card
 #define EF_COUNT_ONLY 8u   // biren's Fit (biren/device.go:190-248): gates end after mutex; the pick has Usedmem 0, Usedcores = Coresreq
 
 struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 64 B

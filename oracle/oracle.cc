@@ -363,7 +363,8 @@ namespace {
 // PLAIN: iluvatar's Fit (iluvatar/device.go:267-371) = the hygon gate list with checkType "key equals the word";
 // COUNT_ONLY: biren's Fit (biren/device.go:190-248) = the gates up to mutex, Usedmem 0, Usedcores as requested
 // AMD: amd/device.go:279-371 — type lists like hygon, whole-card memory by default, cores as a share of the card
-enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY, AMD };
+// MTHREADS: mthreads/device.go:289-405 — the template gates plus customFilterRule (all containers of a pod share one card)
+enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY, AMD, MTHREADS };
 
 struct FitGates {
   Vendor vendor;
@@ -562,6 +563,7 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
           break;
         case Vendor::MLU:
         case Vendor::ASCEND:
+        case Vendor::MTHREADS:     // mthreads/device.go:191-196
         case Vendor::PLAIN:        // iluvatar/device.go:190-195
         case Vendor::COUNT_ONLY:   // biren/device.go:130-135
           found = true;
@@ -631,6 +633,15 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
     if (effectiveTotalCore != 0 && dev->Usedcores == effectiveTotalCore && k.Coresreq == 0) { reason["CardComputeUnitsExhausted"]++; continue; }
     if (g.vendor == Vendor::NVIDIA && dev->Mode == "mig")
       throw std::runtime_error("oracle: MIG devices are outside the restated scope");
+    if (g.vendor == Vendor::MTHREADS && allocated) {
+      // customFilterRule, mthreads/device.go:266-276,362-366: every device an earlier container of this pod got (looked
+      // up under the DEVICE's type string) must be this very device
+      bool ok = true;
+      auto prev = allocated->find(dev->Type);
+      if (prev != allocated->end())
+        for (auto& ctrs : prev->second) for (auto& cd : ctrs) if (cd.UUID != dev->ID) ok = false;
+      if (!ok) { reason["CardNotFoundCustomFilterRule"]++; continue; }
+    }
 
     bool decrement;
     if (g.vendor == Vendor::NVIDIA) decrement = !needTopology;                               // nvidia/device.go:831-833
@@ -716,7 +727,8 @@ class PlainDevices : public Devices {
   FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
                 const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
                 const QuotaManager* quota) const override {
-    FitGates g{v_.FitKind == 1 ? Vendor::COUNT_ONLY : (v_.FitKind == 2 ? Vendor::AMD : Vendor::PLAIN), v_.CommonWord,
+    FitGates g{v_.FitKind == 1 ? Vendor::COUNT_ONLY : (v_.FitKind == 2 ? Vendor::AMD : (v_.FitKind == 3 ? Vendor::MTHREADS : Vendor::PLAIN)),
+               v_.CommonWord,
                v_.UseType, v_.NoUseType, v_.UseUUID, v_.NoUseUUID};
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
@@ -725,6 +737,20 @@ class PlainDevices : public Devices {
     auto it = pd.find(v_.CommonWord);
     if (it != pd.end() && !it->second.empty()) {
       std::string s = EncodePodSingleDevice(it->second);
+      if (v_.FitKind == 3) {
+        // mthreads/device.go:155-177: only the allocated key; the card indices of the LAST container that got devices;
+        // the node again under its own key; a timestamp (blanked, canonical rule 6)
+        annos[v_.Allocated] = s;
+        for (auto& ctr : it->second) {
+          if (ctr.empty()) continue;
+          std::string value;
+          for (auto& d : ctr) { if (!value.empty()) value += ","; value += std::to_string(d.Idx); }
+          annos["mthreads.com/gpu-index"] = value;
+          annos["mthreads.com/predicate-time"] = "";
+          annos["mthreads.com/predicate-node"] = annos["hami.io/vgpu-node"];
+        }
+        return;
+      }
       annos[v_.ToAllocate] = s;
       annos[v_.Allocated] = s;
     }

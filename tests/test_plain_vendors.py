@@ -58,6 +58,42 @@ def test_biren_fit(orc, case):
     assert reason == case["wantReason"]
 
 
+@pytest.mark.parametrize("case", load("mthreads_fit"), ids=[c["name"] for c in load("mthreads_fit")])
+def test_mthreads_fit(orc, case):
+    # mthreads/device_test.go:686-1186
+    annos = case["annos"] if isinstance(case["annos"], dict) else {}
+    fit, got, reason = run_fit(orc, "Mthreads", case["devices"], case["request"], annos)
+    assert fit == case["wantFit"]
+    if fit:
+        assert [g[0] for g in got] == case["wantDevIDs"] and len(got) == case["wantLen"]
+    assert reason == case["wantReason"]
+
+
+def _mthreads_node(name, n):
+    return {"name": name, "devices": [{"id": "%s-mthreads-%d" % (name, d), "index": d, "count": 100, "devmem": 49152, "devcore": 16,
+                                       "type": "Mthreads", "numa": 0, "mode": "", "health": True, "vendor": "Mthreads"} for d in range(n)]}
+
+
+def test_mthreads_containers_of_a_pod_share_one_card():
+    # customFilterRule (mthreads/device.go:266-276; device_test.go:613-684): the second container may only land on the card
+    # the first one got, and the annotation set is mthreads' own (device.go:155-177)
+    o = oa.Oracle("binpack", "spread")
+    o.node_upsert(_mthreads_node("mt-0", 3))
+    req = {"key": "Mthreads", "type": "Mthreads", "nums": 1, "memreq": 1024, "mempct": 0, "coresreq": 4}
+    r = o.filter({"uid": "p1", "ns": "default", "name": "p1", "annotations": {}, "n_init": 0, "containers": [[req], [req], [req]]})
+    assert r["status"] == abi.HS_FIT
+    cards = [c[0][0] for c in r["devices"]["Mthreads"]]
+    assert len(set(cards)) == 1
+    a = r["annotations"]
+    assert "hami.io/mthreads-vgpu-devices-allocated" in a and "hami.io/mthreads-vgpu-devices-to-allocate" not in a
+    assert a["mthreads.com/predicate-node"] == "mt-0" and a["mthreads.com/predicate-time"] == "" and a["mthreads.com/gpu-index"] in "012"
+    # two cards in the first container: no single card can satisfy the rule for the second one
+    two = dict(req, nums=2)
+    r = o.filter({"uid": "p2", "ns": "default", "name": "p2", "annotations": {}, "n_init": 0, "containers": [[two], [req]]})
+    assert r["status"] == abi.HS_NOFIT and "CardNotFoundCustomFilterRule" in r["failed"]["mt-0"]
+    o.close()
+
+
 AMD_CASES = json.load(open(os.path.join(ROOT, "tests", "golden", "ingest_funcs.json")))["amd_fit"]
 
 
@@ -99,7 +135,7 @@ def _cluster(n_nodes, n_pods, seed=11):
     rng = random.Random(seed)
     nodes, kinds = [], []
     for i in range(n_nodes):
-        kind = ("NVIDIA", "MR-V100", "BI-V150", "Biren", "AMD")[i % 5]
+        kind = ("NVIDIA", "MR-V100", "BI-V150", "Biren", "AMD", "Mthreads")[i % 6]
         nd = rng.randrange(2, 9)
         devs = []
         for d in range(nd):
@@ -109,6 +145,9 @@ def _cluster(n_nodes, n_pods, seed=11):
             elif kind == "Biren":
                 devs.append({"id": "BR-%03d-%d" % (i, d), "index": d, "count": rng.choice([1, 1, 2]), "devmem": 0, "devcore": 0,
                              "type": "Biren", "numa": 0, "mode": "", "health": rng.random() > 0.05, "vendor": "Biren"})
+            elif kind == "Mthreads":
+                devs.append({"id": "pv-%03d-mthreads-%d" % (i, d), "index": d, "count": 100, "devmem": 49152, "devcore": 16,
+                             "type": "Mthreads", "numa": 0, "mode": "", "health": True, "vendor": "Mthreads"})
             elif kind == "AMD":
                 devs.append({"id": "AMD-%03d-%d" % (i, d), "index": d, "count": 4, "devmem": 196608, "devcore": rng.choice([64, 100, 304]),
                              "type": rng.choice(["AMD_Instinct_MI300X_VF", "AMD_Instinct_MI250"]), "numa": 0, "mode": "",
@@ -120,7 +159,7 @@ def _cluster(n_nodes, n_pods, seed=11):
         kinds.append(kind)
     ops, live = [], []
     for p in range(n_pods):
-        kind = rng.choice(["NVIDIA", "MR-V100", "BI-V150", "Biren", "Biren", "AMD", "AMD", "MR-V50"])   # MR-V50: registered, no node has it
+        kind = rng.choice(["NVIDIA", "MR-V100", "BI-V150", "Biren", "Biren", "AMD", "AMD", "Mthreads", "Mthreads", "MR-V50"])   # MR-V50: registered, no node has it
         annos = {}
         if rng.random() < 0.3:
             annos["hami.io/gpu-scheduler-policy"] = rng.choice(["binpack", "spread", "mutex"])
@@ -132,6 +171,14 @@ def _cluster(n_nodes, n_pods, seed=11):
             if rng.random() < 0.15:
                 n = rng.choice([x for x, k in zip(nodes, kinds) if k == "Biren"])
                 annos[rng.choice(["birentech.com/use-gpuuuid", "birentech.com/nouse-gpuuuid"])] = n["devices"][0]["id"]
+        elif kind == "Mthreads":
+            req = {"key": kind, "type": kind, "nums": rng.choice([1, 1, 1, 2]), "memreq": rng.choice([0, 1024, 8192]),
+                   "mempct": rng.choice([100, 25]), "coresreq": rng.choice([0, 2, 4, 16])}
+            if req["memreq"]:
+                req["mempct"] = 0
+            if rng.random() < 0.15:
+                n = rng.choice([x for x, k in zip(nodes, kinds) if k == "Mthreads"])
+                annos[rng.choice(["mthreads.ai/use-gpuuuid", "mthreads.ai/nouse-gpuuuid"])] = n["devices"][0]["id"]
         elif kind == "AMD":
             req = {"key": kind, "type": kind, "nums": rng.choice([1, 1, 2, 4]), "memreq": rng.choice([0, 0, 65536, 98304]), "mempct": 0,
                    "coresreq": rng.choice([0, 1, 25, 50, 101])}
@@ -151,7 +198,9 @@ def _cluster(n_nodes, n_pods, seed=11):
                 annos["hami.io/%s-%s-uuid" % (rng.choice(["use", "no-use"]), kind)] = n["devices"][0]["id"]
         uid = "pv-%05d" % p
         ctrs = [[req]]
-        if rng.random() < 0.15:
+        if kind == "Mthreads" and rng.random() < 0.5:      # several containers: customFilterRule ties them to one card
+            ctrs = [[dict(req, nums=rng.choice([1, 1, 2]))] for _ in range(rng.choice([2, 3]))]
+        elif rng.random() < 0.15:
             ctrs.append([dict(req, nums=1)])
         ops.append(("filter", {"uid": uid, "ns": "default", "name": uid, "annotations": annos, "containers": ctrs, "n_init": 0}))
         live.append(uid)
@@ -172,7 +221,9 @@ def test_plain_vendors_gpu_parity():
             k = arg["containers"][0][0]["type"]
             fits[k] = fits.get(k, 0) + 1
     assert fits.get("Biren", 0) > 20 and fits.get("MR-V100", 0) > 20 and fits.get("BI-V150", 0) > 20 and "MR-V50" not in fits
-    assert fits.get("AMD", 0) > 20
+    assert fits.get("AMD", 0) > 20 and fits.get("Mthreads", 0) > 20
+    assert any(r["status"] == abi.HS_NOFIT and any("CardNotFoundCustomFilterRule" in v for v in r["failed"].values())
+               for (kind, arg), r in zip(ops, ref) if kind == "filter")
     amd = next(r for (kind, arg), r in zip(ops, ref) if kind == "filter" and r["status"] == abi.HS_FIT and arg["containers"][0][0]["type"] == "AMD")
     assert ",AMD_Instinct_" in amd["annotations"]["hami.io/amd-devices-allocated"]      # the device's type, not the key
     sample = next(r for (kind, arg), r in zip(ops, ref) if kind == "filter" and r["status"] == abi.HS_FIT and arg["containers"][0][0]["type"] == "Biren")

@@ -332,6 +332,7 @@ IDENTS = {
     "Ascend910CType": "Ascend910C", "Ascend910Prefix": "Ascend910",
     "VNPUModeAnnotation": "huawei.com/vnpu-mode", "VNPUModeHamiCore": "hami-core",
     "VNPUNodeSelectorAnnotation": "hami-vnpu-core",
+    "MthreadsGPUDevice": "Mthreads", "MthreadsUseUUID": "mthreads.ai/use-gpuuuid", "MthreadsNoUseUUID": "mthreads.ai/nouse-gpuuuid",
     "BirenDevice": "Biren", "BirenCommonWord": "Biren",
     "BirenUseUUID": "birentech.com/use-gpuuuid", "BirenNoUseUUID": "birentech.com/nouse-gpuuuid",
 }
@@ -445,6 +446,7 @@ TABLES = [
     ("ascend_generate_requests_range", "pkg/device/ascend/device_test.go", "Test_GenerateResourceRequests_OutOfRangeValues", "tests"),
     ("iluvatar_fit", "pkg/device/iluvatar/device_test.go", "Test_Fit", "tests"),
     ("biren_fit", "pkg/device/biren/device_test.go", "TestDevices_Fit", "tests"),
+    ("mthreads_fit", "pkg/device/mthreads/device_test.go", "TestDevices_Fit", "tests"),
 ]
 
 
