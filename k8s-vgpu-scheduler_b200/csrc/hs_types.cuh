@@ -19,7 +19,7 @@
 // group with 128-bit loads.  32 B per device, 256 B per node.
 //
 // dflags: bit0 health | bit1 cordoned | bit2 present | bits3-5 mode id | bits8-15 NetworkID (255 = none)
-// packed: bits0-7 numa | bits8-13 type id | bits14-21 DeviceInfo.Index | bits22-25 vendor id
+// packed: bits0-7 numa | bits8-13 type id | bits14-21 DeviceInfo.Index | bits22-26 vendor id
 #define DF_HEALTH 1u
 #define DF_CORDON 2u
 #define DF_PRESENT 4u
