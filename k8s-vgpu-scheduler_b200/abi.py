@@ -130,6 +130,8 @@ DEFAULT_VENDORS = [
     # amd/device.go:40-52,62-66
     ("AMD", HS_FIT_AMD, "amd.com/use-gpu-uuid", "amd.com/nouse-gpu-uuid", "hami.io/amd-devices-to-allocate",
      "hami.io/amd-devices-allocated", "amd.com/use-gputype", "amd.com/nouse-gputype"),
+    # vastai in card mode (vastai/device.go:228-291 without DeviceStrategy "die") has biren's gate list
+    ("Vastai", HS_FIT_COUNT_ONLY, "vastaitech.com/use-gpuuuid", "vastaitech.com/nouse-gpuuuid", None, None),
     # mthreads/device.go:44-58,76-80
     ("Mthreads", HS_FIT_MTHREADS, "mthreads.ai/use-gpuuuid", "mthreads.ai/nouse-gpuuuid",
      "hami.io/mthreads-vgpu-devices-to-allocate", "hami.io/mthreads-vgpu-devices-allocated"),

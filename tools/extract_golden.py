@@ -333,6 +333,7 @@ IDENTS = {
     "VNPUModeAnnotation": "huawei.com/vnpu-mode", "VNPUModeHamiCore": "hami-core",
     "VNPUNodeSelectorAnnotation": "hami-vnpu-core",
     "MthreadsGPUDevice": "Mthreads", "MthreadsUseUUID": "mthreads.ai/use-gpuuuid", "MthreadsNoUseUUID": "mthreads.ai/nouse-gpuuuid",
+    "VastaiDevice": "Vastai", "VastaiUseUUID": "vastaitech.com/use-gpuuuid", "VastaiNoUseUUID": "vastaitech.com/nouse-gpuuuid",
     "BirenDevice": "Biren", "BirenCommonWord": "Biren",
     "BirenUseUUID": "birentech.com/use-gpuuuid", "BirenNoUseUUID": "birentech.com/nouse-gpuuuid",
 }
@@ -447,6 +448,7 @@ TABLES = [
     ("iluvatar_fit", "pkg/device/iluvatar/device_test.go", "Test_Fit", "tests"),
     ("biren_fit", "pkg/device/biren/device_test.go", "TestDevices_Fit", "tests"),
     ("mthreads_fit", "pkg/device/mthreads/device_test.go", "TestDevices_Fit", "tests"),
+    ("vastai_fit", "pkg/device/vastai/device_test.go", "TestDevices_Fit", "tests"),
 ]
 
 
