@@ -220,7 +220,10 @@ enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
         * device an earlier container of the pod received must be the candidate itself, reason
         * "CardNotFoundCustomFilterRule"; PatchAnnotations (:155-177) writes only the allocated key plus
         * mthreads.com/gpu-index, mthreads.com/predicate-node and mthreads.com/predicate-time (returned empty)         */
-       HS_FIT_MTHREADS = 3 };
+       HS_FIT_MTHREADS = 3,
+       /* enflame GCU, whole cards (pkg/device/enflame/gcu.go:144-183): health, type, and a card in use at all is an
+        * "ExclusiveDeviceAllocateConflict"; no uuid lists, no slot count; the pick records Memreq and Coresreq as asked */
+       HS_FIT_WHOLE_CARD = 4 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */

@@ -137,6 +137,7 @@ struct VendorInfo {
   bool ascend = false, ascend910 = false;
   int gate = 0;             // device-side gate class (HV_*): plain vendors share hygon's gate list (HV_DCU)
   bool count_only = false;  // biren's Fit: no memory / core gates (EF_COUNT_ONLY)
+  bool whole_card = false;  // enflame GCU's Fit: a card in use at all is a conflict (EF_WHOLE_CARD)
   bool mthreads = false;    // mthreads' Fit: template gates + customFilterRule; its own annotation set (EF_MTHREADS)
   bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
@@ -631,6 +632,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       if (v && v->count_only) e.flags |= EF_COUNT_ONLY;
       if (v && v->amd) e.flags |= EF_AMD;
       if (v && v->mthreads) e.flags |= EF_MTHREADS;
+      if (v && v->whole_card) e.flags |= EF_WHOLE_CARD;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
       if (v && v->ascend910) e.flags |= EF_ASCEND910;
@@ -671,7 +673,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     const DevEntry& e = c.entries[0];
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
               !(e.flags & EF_ASCEND910)) ? 1 : 0;
-    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS))) p.fast = 0;
+    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD))) p.fast = 0;
   }
   quota_rows_for(h, c.meta.ns, p);
   if (p.q_idx[0] >= 0 || p.q_idx[1] >= 0) p.fast = 0;   // the quota check lives in the general evaluator (hs_eval.cuh)
@@ -1415,6 +1417,7 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.count_only = vc.fit_kind == HS_FIT_COUNT_ONLY;
       v.amd = vc.fit_kind == HS_FIT_AMD;
       v.mthreads = vc.fit_kind == HS_FIT_MTHREADS;
+      v.whole_card = vc.fit_kind == HS_FIT_WHOLE_CARD;
       if (vc.use_type_key) v.use_type = vc.use_type_key;
       if (vc.nouse_type_key) v.nouse_type = vc.nouse_type_key;
       if (vc.use_uuid_key) v.use_uuid = vc.use_uuid_key;

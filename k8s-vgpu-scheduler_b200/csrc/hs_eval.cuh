@@ -234,7 +234,7 @@ __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e,
   int prevnuma = -1;
   fc.ntmp = 0;
   const bool countOnly = e.flags & EF_COUNT_ONLY;
-  fc.cores = (e.coresreq > 100 && !countOnly) ? 100 : e.coresreq;
+  fc.cores = (e.coresreq > 100 && !countOnly && !(e.flags & EF_WHOLE_CARD)) ? 100 : e.coresreq;   // biren / GCU record Coresreq as asked
   const bool isMutex = pod.flags & PF_MUTEX;
   bool needTopology = isNv && (pod.flags & PF_TOPOLOGY);
   const bool isHAMiCore = isAscend && (pod.flags & PF_ASCEND_HAMICORE);
@@ -270,6 +270,17 @@ __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e,
     bool found = (e.type_allow >> PK_TYPE(pk)) & 1ull;
     if (isNv && !((e.mode_allow >> DF_MODE(df)) & 1u)) found = false;
     if (!found) { REASON(0); continue; }
+    if (e.flags & EF_WHOLE_CARD) {        // enflame/gcu.go:159-176: a card in use at all is a conflict; no uuid / slot gates
+      if (w.used[d] > 0) { REASON(9); continue; }
+      if (k_nums > 0) {
+        k_nums--;
+        fc.tmp_dev[fc.ntmp] = d;
+        fc.tmp_mem[fc.ntmp] = e.memreq;
+        fc.ntmp++;
+      }
+      if (k_nums == 0) return true;
+      continue;
+    }
     const int numa = PK_NUMA(pk);
     if (numaAssert && prevnuma != numa) {
       if (k_nums != origin) { if (MODE == EV_EXPLAIN) out.reasons[8] += (uint32_t)fc.ntmp; }

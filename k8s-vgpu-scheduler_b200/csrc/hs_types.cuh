@@ -49,7 +49,8 @@ enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
 #define EF_ASCEND910 1u     // CommonWord has prefix "Ascend910": NetworkID topology + ScoreNode
 #define EF_ASCEND910C 2u    // k.Type == "Ascend910C": module pairing
 #define EF_MIGMODE_OK 4u    // pod's vgpu-mode annotation is absent or contains "mig" (isMIGRequest)
-#define EF_MTHREADS 32u     // mthreads' Fit (mthreads/device.go:289-405): template gates + customFilterRule (one card per pod)
+#define EF_WHOLE_CARD 64u   // enflame GCU's Fit (enflame/gcu.go:144-183): health, type, "in use at all" = conflict; no uuid lists, no slot count
+#define EF_MTHREADS 32u    // mthreads' Fit (mthreads/device.go:289-405): template gates + customFilterRule (one card per pod)
 #define EF_AMD 16u         // amd's Fit (amd/device.go:279-371): whole-card memory by default, cores as a share of the card
 #define EF_COUNT_ONLY 8u   // biren's Fit (biren/device.go:190-248): gates end after mutex; the pick has Usedmem 0, Usedcores = Coresreq
 

@@ -364,7 +364,8 @@ namespace {
 // COUNT_ONLY: biren's Fit (biren/device.go:190-248) = the gates up to mutex, Usedmem 0, Usedcores as requested
 // AMD: amd/device.go:279-371 — type lists like hygon, whole-card memory by default, cores as a share of the card
 // MTHREADS: mthreads/device.go:289-405 — the template gates plus customFilterRule (all containers of a pod share one card)
-enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY, AMD, MTHREADS };
+// WHOLE_CARD: enflame GCU (enflame/gcu.go:144-183) — health, type, "in use at all" = conflict; no uuid lists, no slot count
+enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY, AMD, MTHREADS, WHOLE_CARD };
 
 struct FitGates {
   Vendor vendor;
@@ -563,6 +564,7 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
           break;
         case Vendor::MLU:
         case Vendor::ASCEND:
+        case Vendor::WHOLE_CARD:   // enflame/gcu.go:202-204
         case Vendor::MTHREADS:     // mthreads/device.go:191-196
         case Vendor::PLAIN:        // iluvatar/device.go:190-195
         case Vendor::COUNT_ONLY:   // biren/device.go:130-135
@@ -571,6 +573,17 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
       }
     }
     if (!found) { reason["CardTypeMismatch"]++; continue; }
+    if (g.vendor == Vendor::WHOLE_CARD) {     // enflame/gcu.go:159-176
+      if (dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+      if (k.Nums > 0) {
+        k.Nums--;
+        ContainerDevice cd;
+        cd.Idx = (int)dev->Index; cd.UUID = dev->ID; cd.Type = k.Type; cd.Usedmem = k.Memreq; cd.Usedcores = k.Coresreq;
+        tmpDevs.push_back(cd);
+      }
+      if (k.Nums == 0) { FitResult r; r.fit = true; r.devs = tmpDevs; return r; }
+      continue;
+    }
     if (numa && prevnuma != dev->Numa) {
       if (k.Nums != originReq) reason["NumaNotFit"] += (int)tmpDevs.size();
       k.Nums = originReq;
@@ -727,7 +740,8 @@ class PlainDevices : public Devices {
   FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
                 const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
                 const QuotaManager* quota) const override {
-    FitGates g{v_.FitKind == 1 ? Vendor::COUNT_ONLY : (v_.FitKind == 2 ? Vendor::AMD : (v_.FitKind == 3 ? Vendor::MTHREADS : Vendor::PLAIN)),
+    static const Vendor kinds[] = {Vendor::PLAIN, Vendor::COUNT_ONLY, Vendor::AMD, Vendor::MTHREADS, Vendor::WHOLE_CARD};
+    FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 4 ? v_.FitKind : 0],
                v_.CommonWord,
                v_.UseType, v_.NoUseType, v_.UseUUID, v_.NoUseUUID};
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());

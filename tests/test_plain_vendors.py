@@ -83,6 +83,17 @@ def test_vastai_fit_card_mode(orc, case):
     assert reason == case["wantReason"]
 
 
+@pytest.mark.parametrize("case", load("gcu_fit"), ids=[c["name"] for c in load("gcu_fit")])
+def test_enflame_gcu_fit(orc, case):
+    # enflame/gcu_test.go:433-677: whole cards — a card in use at all is a conflict
+    fit, got, reason = run_fit(orc, "GCU", case["devices"], case["request"], {})
+    assert fit == case["wantFit"]
+    if fit:
+        assert [g[0] for g in got] == case["wantDevIDs"] and len(got) == case["wantLen"]
+        assert all((g[2], g[3]) == (case["request"]["Memreq"], case["request"]["Coresreq"]) for g in got)
+    assert reason == case["wantReason"]
+
+
 def _mthreads_node(name, n):
     return {"name": name, "devices": [{"id": "%s-mthreads-%d" % (name, d), "index": d, "count": 100, "devmem": 49152, "devcore": 16,
                                        "type": "Mthreads", "numa": 0, "mode": "", "health": True, "vendor": "Mthreads"} for d in range(n)]}
@@ -149,13 +160,16 @@ def _cluster(n_nodes, n_pods, seed=11):
     rng = random.Random(seed)
     nodes, kinds = [], []
     for i in range(n_nodes):
-        kind = ("NVIDIA", "MR-V100", "BI-V150", "Biren", "AMD", "Mthreads", "Vastai")[i % 7]
+        kind = ("NVIDIA", "MR-V100", "BI-V150", "Biren", "AMD", "Mthreads", "Vastai", "GCU")[i % 8]
         nd = rng.randrange(2, 9)
         devs = []
         for d in range(nd):
             if kind == "NVIDIA":
                 devs.append({"id": "GPU-%03d-%d" % (i, d), "index": d, "count": 10, "devmem": 81920, "devcore": 100,
                              "type": "NVIDIA A100-SXM4-80GB", "numa": d // 4, "mode": "hami-core", "health": True, "vendor": "NVIDIA"})
+            elif kind == "GCU":
+                devs.append({"id": "GCU-%03d-%d" % (i, d), "index": d, "count": 1, "devmem": 49152, "devcore": 100,
+                             "type": "GCU", "numa": 0, "mode": "", "health": rng.random() > 0.05, "vendor": "GCU"})
             elif kind in ("Biren", "Vastai"):
                 devs.append({"id": "%s-%03d-%d" % (kind[:2].upper(), i, d), "index": d, "count": rng.choice([1, 1, 2]), "devmem": 0,
                              "devcore": 0, "type": kind, "numa": 0, "mode": "", "health": rng.random() > 0.05, "vendor": kind})
@@ -173,13 +187,16 @@ def _cluster(n_nodes, n_pods, seed=11):
         kinds.append(kind)
     ops, live = [], []
     for p in range(n_pods):
-        kind = rng.choice(["NVIDIA", "MR-V100", "BI-V150", "Biren", "Biren", "Vastai", "AMD", "AMD", "Mthreads", "Mthreads", "MR-V50"])   # MR-V50: registered, no node has it
+        kind = rng.choice(["NVIDIA", "MR-V100", "BI-V150", "Biren", "Biren", "Vastai", "GCU", "AMD", "AMD", "Mthreads", "Mthreads", "MR-V50"])   # MR-V50: registered, no node has it
         annos = {}
         if rng.random() < 0.3:
             annos["hami.io/gpu-scheduler-policy"] = rng.choice(["binpack", "spread", "mutex"])
         if rng.random() < 0.3:
             annos["hami.io/node-scheduler-policy"] = rng.choice(["binpack", "spread"])
-        if kind in ("Biren", "Vastai"):
+        if kind == "GCU":
+            req = {"key": kind, "type": kind, "nums": rng.choice([1, 1, 2, 4]), "memreq": rng.choice([0, 100, 49152]), "mempct": 100,
+                   "coresreq": rng.choice([0, 100, 150])}
+        elif kind in ("Biren", "Vastai"):
             req = {"key": kind, "type": kind, "nums": rng.choice([1, 1, 2, 3]), "memreq": rng.choice([0, 512]), "mempct": 0,
                    "coresreq": rng.choice([0, 20, 150])}
             if rng.random() < 0.15:
@@ -236,7 +253,7 @@ def test_plain_vendors_gpu_parity():
             k = arg["containers"][0][0]["type"]
             fits[k] = fits.get(k, 0) + 1
     assert fits.get("Biren", 0) > 20 and fits.get("MR-V100", 0) > 20 and fits.get("BI-V150", 0) > 20 and "MR-V50" not in fits
-    assert fits.get("AMD", 0) > 20 and fits.get("Mthreads", 0) > 20 and fits.get("Vastai", 0) > 10
+    assert fits.get("AMD", 0) > 20 and fits.get("Mthreads", 0) > 20 and fits.get("Vastai", 0) > 10 and fits.get("GCU", 0) > 10
     assert any(r["status"] == abi.HS_NOFIT and any("CardNotFoundCustomFilterRule" in v for v in r["failed"].values())
                for (kind, arg), r in zip(ops, ref) if kind == "filter")
     amd = next(r for (kind, arg), r in zip(ops, ref) if kind == "filter" and r["status"] == abi.HS_FIT and arg["containers"][0][0]["type"] == "AMD")

@@ -334,6 +334,7 @@ IDENTS = {
     "VNPUNodeSelectorAnnotation": "hami-vnpu-core",
     "MthreadsGPUDevice": "Mthreads", "MthreadsUseUUID": "mthreads.ai/use-gpuuuid", "MthreadsNoUseUUID": "mthreads.ai/nouse-gpuuuid",
     "VastaiDevice": "Vastai", "VastaiUseUUID": "vastaitech.com/use-gpuuuid", "VastaiNoUseUUID": "vastaitech.com/nouse-gpuuuid",
+    "EnflameGCUDevice": "GCU",
     "BirenDevice": "Biren", "BirenCommonWord": "Biren",
     "BirenUseUUID": "birentech.com/use-gpuuuid", "BirenNoUseUUID": "birentech.com/nouse-gpuuuid",
 }
@@ -449,6 +450,7 @@ TABLES = [
     ("biren_fit", "pkg/device/biren/device_test.go", "TestDevices_Fit", "tests"),
     ("mthreads_fit", "pkg/device/mthreads/device_test.go", "TestDevices_Fit", "tests"),
     ("vastai_fit", "pkg/device/vastai/device_test.go", "TestDevices_Fit", "tests"),
+    ("gcu_fit", "pkg/device/enflame/gcu_test.go", "TestGCUDevices_Fit", "tests"),
 ]
 
 
