@@ -315,7 +315,27 @@ def run_reference(args):
     threads = ncpu()
     step_ops = args.ref_ops
     prefill = args.ref_prefill
-    cfg, nodes, fill, batches = make_stream(args.steps, args.warmup, args.nodes, prefill, step_ops)
+    multi = args.gpus > 1 or int(os.environ.get("WORLD_SIZE", "1")) > 1
+    if multi:
+        # the arm's config at N > 1 is C5 (bench_multi.py): the same 100,000-node inventory and fill, a smaller sample
+        import bench_multi as BM
+        import k8s_vgpu_scheduler_b200.gen as gen
+        step_ops = 4            # one Filter over 100,000 nodes takes the host a few hundred ms: keep the sample bounded
+        prefill = 128           # (the GPU arm fills with BM.FILL_FILTERS; the CPU arm could not do that within minutes)
+        n_nodes = BM.N_NODES
+        cfg, nodes, ops = gen.config5(n_nodes=n_nodes, n_pods=prefill + (args.warmup + args.steps + 1) * step_ops)
+        cnt, cut = 0, 0
+        for i, (k, _) in enumerate(ops):
+            if k == "filter":
+                cnt += 1
+                if cnt == prefill:
+                    cut = i + 1
+                    break
+        fill, rest = ops[:cut], ops[cut:]
+        batches = [rest[i * step_ops:(i + 1) * step_ops] for i in range(args.warmup + args.steps)]
+    else:
+        n_nodes = args.nodes
+        cfg, nodes, fill, batches = make_stream(args.steps, args.warmup, args.nodes, prefill, step_ops)
     o = oa.Oracle(cfg["node_policy"], cfg["gpu_policy"], faithful=False, threads=threads)
     for n in nodes:
         o.node_upsert(n)
@@ -331,13 +351,15 @@ def run_reference(args):
         decisions += sum(1 for k, _ in batches[i] if k == "filter")
     o.close()
     value = decisions / sum(secs)
-    sample = ("%d ops per step of the C3 stream after %d prefill filters; oracle (C++ restatement of the reference) in "
+    sample = ("%d ops per step of the %s stream after %d prefill filters; oracle (C++ restatement of the reference) in "
               "its faithful shape: usage rebuilt from the whole pod cache per Filter, %d threads over node chunks"
-              % (step_ops, prefill, threads))
+              % (step_ops, "C5" if multi else "C3", prefill, threads))
     out = {"impl": "reference", "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * statistics.mean(secs), 3),
-           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32+f32", "data": "synthetic",
-           "config": {"workload": "C3: %d nodes x 8 x 180 GB, topology-aware 2/4/8-GPU pods (bounded sample)" % args.nodes,
+           "higher_is_better": True, "scaling": "strong" if multi else "weak", "vs_baseline": None, "dtype": "int32+f32",
+           "data": "synthetic",
+           "config": {"workload": ("C5: %d-node inventory (C2 device/request mix), one host, no sharding (bounded sample)" % n_nodes) if multi
+                      else ("C3: %d nodes x 8 x 180 GB, topology-aware 2/4/8-GPU pods (bounded sample)" % n_nodes),
                       "ops_per_step": step_ops},
            "cpu_baseline": {"value": round(value, 2), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
            "e2e": {"value": round(value, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
