@@ -281,6 +281,8 @@ struct hs_handle {
   double prof_s[4] = {0, 0, 0, 0};      // fit / no-fit / other / count
   double host_s[4] = {0, 0, 0, 0};      // diagnostic: cumulative host seconds in compile / device+copies / absorb / summary
   uint32_t fail_cap = 32;
+  uint32_t fail_cap_now = 32;           // no-fit decisions one launch can hold before the host drains the reasons
+  bool fail_cap_fixed = false;          // HS_FAIL_CAP given: use it as is (tests of the drain-and-resume path)
   std::vector<OpMeta> metas;            // per device op
   std::vector<int> user_first_op;       // per caller op: index of its FILTER/RELEASE device op
   std::vector<int> user_status;
@@ -776,7 +778,7 @@ int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_ca
   ka.n_ops = n_ops;
   ka.decisions = h->b_dec.d; ka.allocs = h->b_alloc.d; ka.alloc_cap = alloc_cap;
   ka.commit_delta = h->b_delta.d; ka.sync = h->b_best.d;
-  ka.fail = h->b_fail.d; ka.fail_cap = h->fail_cap;
+  ka.fail = h->b_fail.d; ka.fail_cap = h->fail_cap_now;
   ka.counters = h->b_counters.d;
   ka.pos_base = (int32_t)h->pos_base;
   ka.timing = h->timing ? h->b_timing.d : nullptr;
@@ -797,8 +799,15 @@ int run_device_ops(hs_handle* h, int n_ops, size_t n_entries, size_t n_uuid, siz
   int rc = flush_inventory(h);
   if (rc != HS_OK) return rc;
   const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
+  // A no-fit decision leaves 16 B per node; a launch stops when the buffer is full and the host drains it.  Up to 32 MB
+  // of it, so a batch normally runs in ONE launch; the fused multi-GPU path keeps the fixed size, because every rank
+  // must stop at the same op and the shards differ in size.
+  h->fail_cap_now = h->fail_cap;
+  if (!h->fail_cap_fixed && !h->xgpu_connected)
+    h->fail_cap_now = (uint32_t)std::min<size_t>((size_t)std::max(n_ops, 1),
+                                                 std::max<size_t>(h->fail_cap, (32u << 20) / ((size_t)std::max(n_nodes, HS_TILE) * sizeof(DevFail))));
   if (!h->b_dec.ensure(n_ops) || !h->b_alloc.ensure(std::max<uint32_t>(alloc_cap, 1)) || !h->b_delta.ensure((size_t)n_ops * HS_D) ||
-      !h->b_best.ensure((size_t)n_ops * 2) || !h->b_counters.ensure(8) || !h->b_fail.ensure((size_t)h->fail_cap * std::max(n_nodes, HS_TILE))) {
+      !h->b_best.ensure((size_t)n_ops * 2) || !h->b_counters.ensure(8) || !h->b_fail.ensure((size_t)h->fail_cap_now * std::max(n_nodes, HS_TILE))) {
     h->err = "out of device memory for batch buffers";
     return HS_ERR_CUDA;
   }
@@ -1434,7 +1443,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   h->hostprof = getenv("HS_HOSTPROF") != nullptr;
   if (getenv("HS_TIMING") && h->b_timing.ensure(16)) { h->timing = true; cudaMemset(h->b_timing.d, 0, 16 * sizeof(unsigned long long)); }
   const char* fc = getenv("HS_FAIL_CAP");
-  if (fc && atoi(fc) > 0) h->fail_cap = (uint32_t)atoi(fc);
+  if (fc && atoi(fc) > 0) { h->fail_cap = (uint32_t)atoi(fc); h->fail_cap_fixed = true; }
   if (grow_inventory(h, cfg && cfg->reserve_nodes ? (int)cfg->reserve_nodes : HS_TILE) != HS_OK) {
     g_create_error = h->err;
     delete h;

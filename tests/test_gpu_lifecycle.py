@@ -27,6 +27,18 @@ def _decision(r):
     return (r["status"], r.get("failed"))
 
 
+def test_small_reason_buffer_drains_and_resumes(monkeypatch):
+    """With room for only 5 no-fit decisions per launch the engine must stop, hand the reasons to the host and resume at
+    the right op, many times per batch, without changing a single decision."""
+    import k8s_vgpu_scheduler_b200.gen as gen
+    monkeypatch.setenv("HS_FAIL_CAP", "5")
+    for cfg, nodes, ops in (gen.config1(n_pods=400, departures=0.2), gen.mixed_features(n_nodes=16, n_pods=500)):
+        ref, rsnap = parity.run_oracle(cfg, nodes, ops)
+        got, gsnap = parity.run_engine(cfg, nodes, ops, chunk=170)
+        assert sum(1 for r in ref if r.get("status") == abi.HS_NOFIT) > 40
+        assert parity.compare(ops, ref, got, rsnap, gsnap) == []
+
+
 def test_node_reregisters_with_reordered_and_replaced_devices():
     """A node re-registers while pods are bound to it: same UUIDs in another order keep their usage and the pods release
     against the right devices; a replaced UUID starts empty and the share of the pods that sat on the old one is gone."""
