@@ -39,6 +39,25 @@ def test_small_reason_buffer_drains_and_resumes(monkeypatch):
         assert parity.compare(ops, ref, got, rsnap, gsnap) == []
 
 
+def test_long_batches_compiled_in_chunks_under_the_device(monkeypatch):
+    """hs_run_batch compiles a long batch in chunks while the device runs the previous chunk.  With a chunk of 50 ops
+    (and a reason buffer of 3) a 700-op batch crosses many chunk borders: releases that refer to decisions of earlier
+    chunks, re-filtered pods, drained reason buffers in the middle of a chunk — no decision may change."""
+    import k8s_vgpu_scheduler_b200.gen as gen
+    monkeypatch.setenv("HS_PIPE_CHUNK", "50")
+    monkeypatch.setenv("HS_FAIL_CAP", "3")
+    for cfg, nodes, ops in (gen.mixed_features(n_nodes=24, n_pods=700), gen.config3(n_nodes=150, n_pods=900),
+                            gen.config1(n_pods=500, departures=0.3)):
+        ref, rsnap = parity.run_oracle(cfg, nodes, ops)
+        got, gsnap = parity.run_engine(cfg, nodes, ops)          # one batch
+        assert parity.compare(ops, ref, got, rsnap, gsnap) == []
+    monkeypatch.delenv("HS_FAIL_CAP")
+    cfg, nodes, ops = gen.config4(n_nodes=300, n_pods=2500)
+    ref, rsnap = parity.run_oracle(cfg, nodes, ops)
+    got, gsnap = parity.run_engine(cfg, nodes, ops)
+    assert parity.compare(ops, ref, got, rsnap, gsnap) == []
+
+
 def test_node_reregisters_with_reordered_and_replaced_devices():
     """A node re-registers while pods are bound to it: same UUIDs in another order keep their usage and the pods release
     against the right devices; a replaced UUID starts empty and the share of the pods that sat on the old one is gone."""
