@@ -282,7 +282,7 @@ struct hs_handle {
   double prof_s[4] = {0, 0, 0, 0};      // fit / no-fit / other / count
   double host_s[4] = {0, 0, 0, 0};      // diagnostic: cumulative host seconds in compile / device+copies / absorb / summary
   uint32_t fail_cap = 32;
-  uint32_t pipe_chunk = 1024;
+  uint32_t pipe_chunk = 2048;
   int sync2_base = 0;                   // first quota-barrier slot in b_best (== op capacity of the current batch)
   int grid_now = 1;                     // grid of the decide kernel for the current batch
   uint32_t fail_cap_now = 32;           // no-fit decisions one launch can hold before the host drains the reasons
@@ -1388,8 +1388,8 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
   // Long batches on the plain single-GPU path are compiled in chunks: while the device runs chunk c, the host compiles
   // chunk c+1 (op indices, in-batch references and the allocation offsets are batch-wide, so the chunks are one stream
   // to the kernel).  Quota rows are gathered by the compile and uploaded once, so quota'd handles take one chunk.
-  const uint32_t kChunk = h->pipe_chunk;   // 1024 user ops; HS_PIPE_CHUNK overrides (tests)
-  const bool pipelined = !launch_per_op && h->shard_world <= 1 && !h->have_cand && !h->dry_run && !h->any_quota_limit && n_ops >= 2 * kChunk;
+  const uint32_t kChunk = h->pipe_chunk;   // 2048 user ops; HS_PIPE_CHUNK overrides (tests)
+  const bool pipelined = !launch_per_op && h->shard_world <= 1 && !h->have_cand && !h->dry_run && !h->any_quota_limit && n_ops > kChunk;
   if (!pipelined) {
     compile_range(0, n_ops);
     int n = (int)pods.size();
