@@ -366,13 +366,21 @@ int32_t hs_generate_requests(const hs_vendor_resources* vendors, uint32_t n_vend
  * The reference learns a node's devices from register annotations and a pod's committed allocation from its
  * "<vendor>-devices-allocated" annotations; these entry points take the annotation STRINGS.                */
 enum { HS_REG_CSV = 0,    /* device.DecodeNodeDevices  (pkg/device/devices.go:317-381): DCU, iluvatar      */
-       HS_REG_JSON = 1 }; /* device.UnMarshalNodeDevices (pkg/device/devices.go:445-449): NVIDIA, Ascend, … */
+       HS_REG_JSON = 1,   /* device.UnMarshalNodeDevices (pkg/device/devices.go:445-449): NVIDIA, Ascend, … */
+       /* no annotation at all: the devices are derived from the node's CAPACITY (capacity_cores / capacity_memory =
+        * AsInt64 of Status.Capacity[<cores resource>] / [<memory resource>]) and named after the node:               */
+       HS_REG_CAPACITY_MLU = 2,      /* cambricon/device.go:209-232: one card per 100 cores, <node>-cambricon-mlu-<i>   */
+       HS_REG_CAPACITY_MTHREADS = 3  /* mthreads/device.go:130-153: one card per 16 cores, <node>-mthreads-<i>          */
+};
 
 typedef struct hs_vendor_registration {
   const char* vendor;       /* CommonWord(); becomes DeviceInfo.DeviceVendor of every decoded device          */
   int32_t     format;       /* HS_REG_*                                                                      */
   const char* annotation;   /* value of the vendor's node register annotation (e.g. hami.io/node-nvidia-register) */
   const char* pair_scores;  /* value of hami.io/node-nvidia-score, NULL = absent (nvidia/device.go:319-340)   */
+  const char* node_name;    /* HS_REG_CAPACITY_*: the node's name (device IDs are built from it); hs_node_register fills it in */
+  int64_t     capacity_cores;
+  int64_t     capacity_memory;
 } hs_vendor_registration;
 
 /* One ContainerDevice of a decoded / collapsed PodDevices (devices.go:205-216): uuid NULL marks an EMPTY

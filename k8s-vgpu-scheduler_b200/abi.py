@@ -30,7 +30,8 @@ class hs_node_info(C.Structure):
 
 
 class hs_vendor_registration(C.Structure):
-    _fields_ = [("vendor", C.c_char_p), ("format", C.c_int32), ("annotation", C.c_char_p), ("pair_scores", C.c_char_p)]
+    _fields_ = [("vendor", C.c_char_p), ("format", C.c_int32), ("annotation", C.c_char_p), ("pair_scores", C.c_char_p),
+                ("node_name", C.c_char_p), ("capacity_cores", C.c_int64), ("capacity_memory", C.c_int64)]
 
 
 class hs_pod_device(C.Structure):
@@ -43,7 +44,7 @@ class hs_sim_node(C.Structure):
                 ("device_cordon", C.c_char_p), ("hami_vnpu_core", C.c_int8)]
 
 
-HS_REG_CSV, HS_REG_JSON = 0, 1
+HS_REG_CSV, HS_REG_JSON, HS_REG_CAPACITY_MLU, HS_REG_CAPACITY_MTHREADS = 0, 1, 2, 3
 
 
 class hs_container_request(C.Structure):

@@ -359,6 +359,29 @@ bool decode_node_json(const std::string& s, std::vector<Device>& out, std::strin
   return true;
 }
 
+// ---- vendors without a register annotation: devices derived from the node's capacity -----------------------
+bool devices_from_capacity(int kind, const std::string& node, int64_t cores, int64_t memory, std::vector<Device>& out, std::string& err) {
+  out.clear();
+  const bool mlu = kind == 0;
+  if (cores == 0) { err = std::string("device not found ") + (mlu ? "cambricon.com/mlu.smlu.vcore" : "mthreads.com/sgpu-core"); return false; }
+  const int64_t per_card = mlu ? 100 : 16;                 // cores of one card
+  const int64_t factor = mlu ? 256 : 512;                  // MemoryFactor (cambricon/device.go:60, mthreads/device.go:57)
+  for (int64_t i = 0; i * per_card < cores; i++) {
+    Device d;
+    d.index = (uint32_t)i;
+    d.id = node + (mlu ? "-cambricon-mlu-" : "-mthreads-") + std::to_string(i);
+    d.count = 100;
+    d.devmem = (int32_t)((int64_t)((uint64_t)memory * (uint64_t)factor * (uint64_t)per_card) / cores);   // Go: wrapping int64, then int32()
+    d.devcore = (int32_t)per_card;
+    d.type = mlu ? "MLU" : "Mthreads";
+    d.numa = 0;
+    d.health = true;
+    out.push_back(d);
+    if (out.size() > 4096) { err = "capacity yields more than 4096 cards"; out.clear(); return false; }
+  }
+  return true;
+}
+
 // ---- device.DecodePairScores (devices.go:383-389) + the fit loop of GetNodeDevices (nvidia/device.go:319-340)
 // DevicePairScores = []DevicePairScore{ID `json:"uuid"`, Scores map[string]int `json:"score"`}; the FIRST record whose
 // uuid equals a device's ID is attached to it; a device without a record keeps an empty score map (all 0).

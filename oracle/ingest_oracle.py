@@ -260,6 +260,38 @@ def app_containers_only_device_usage(n_init, raw):
     return out
 
 
+def _i64(v):
+    v &= (1 << 64) - 1
+    return v - (1 << 64) if v >> 63 else v
+
+
+def _i32(v):
+    v &= (1 << 32) - 1
+    return v - (1 << 32) if v >> 31 else v
+
+
+def _go_div(a, b):
+    q = abs(a) // abs(b)
+    return q if (a < 0) == (b < 0) else -q
+
+
+def capacity_node_devices(vendor, node, cores, memory):
+    """GetNodeDevices of the two vendors that register through node CAPACITY instead of an annotation:
+    cambricon (pkg/device/cambricon/device.go:209-232) and mthreads (pkg/device/mthreads/device.go:130-153).
+    cores / memory = AsInt64 of Status.Capacity[<cores resource>] / [<memory resource>] (0 when absent)."""
+    per_card, factor, infix, res = {"MLU": (100, 256, "-cambricon-mlu-", "cambricon.com/mlu.smlu.vcore"),
+                                    "Mthreads": (16, 512, "-mthreads-", "mthreads.com/sgpu-core")}[vendor]
+    if cores == 0:
+        raise ValueError("device not found " + res)
+    out, i = [], 0
+    while i * per_card < cores:
+        out.append({"Index": i, "ID": "%s%s%d" % (node, infix, i), "Count": 100,
+                    "Devmem": _i32(_go_div(_i64(memory * factor * per_card), cores)), "Devcore": per_card, "Type": vendor,
+                    "Numa": 0, "Health": True, "DeviceVendor": vendor})
+        i += 1
+    return out
+
+
 def encode_node_devices(devs):
     """device.EncodeNodeDevices, pkg/device/devices.go:391-417 (used for round-trip checks)."""
     return "".join("%s,%d,%d,%d,%s,%d,%s,%d,%s:" % (d["ID"], d["Count"], d["Devmem"], d["Devcore"], d["Type"], d["Numa"],

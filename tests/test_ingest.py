@@ -190,6 +190,45 @@ def test_nvidia_get_node_devices_golden(impl):
             assert m[w["device"] * len(devs) + j] == w["score"]
 
 
+_CAP_FMT = {"MLU": abi.HS_REG_CAPACITY_MLU, "Mthreads": abi.HS_REG_CAPACITY_MTHREADS}
+_CAP_KEYS = ("Index", "ID", "Count", "Devmem", "Devcore", "Type", "Numa", "Health", "DeviceVendor")
+
+
+def _capacity_product(vendor, node, cores, memory):
+    try:
+        devs, _ = eng.decode_node_devices(vendor, _CAP_FMT[vendor], None, None, node, cores, memory)
+        return [{k: d[k] for k in _CAP_KEYS} for d in devs], None
+    except eng.IngestError as e:
+        return None, str(e)
+
+
+def test_capacity_node_devices_golden():
+    """cambricon / mthreads Test_GetNodeDevices: oracle and product against the reference's own expectations."""
+    cases = gold("ingest_funcs")["capacity_node_devices"]
+    assert {c["vendor"] for c in cases} == {"MLU", "Mthreads"}
+    for c in cases:
+        assert c["want"], c["name"]
+        assert O.capacity_node_devices(c["vendor"], c["node"], c["cores"], c["memory"]) == c["want"], c["source"]
+        got, err = _capacity_product(c["vendor"], c["node"], c["cores"], c["memory"])
+        assert err is None and got == c["want"], c["source"]
+
+
+def test_capacity_node_devices_product_vs_oracle():
+    rng = random.Random(77)
+    for vendor in ("MLU", "Mthreads"):
+        for _ in range(300):
+            cores = rng.choice([0, 1, 15, 16, 17, 99, 100, 101, 800, 1600, 128, -5, rng.randrange(1, 3000)])
+            memory = rng.choice([0, 1, 1536, 96, 2 ** 31, 2 ** 52, -7, rng.randrange(0, 1 << 20)])
+            node = "n%d" % rng.randrange(100)
+            got, err = _capacity_product(vendor, node, cores, memory)
+            try:
+                want = O.capacity_node_devices(vendor, node, cores, memory)
+            except ValueError as e:
+                assert got is None and str(e) in err
+                continue
+            assert got == want, (vendor, cores, memory)
+
+
 # ---- 3: product vs oracle, seeded random inputs -------------------------------------------------------
 def _rand_csv(rng):
     n = rng.randrange(0, 5)

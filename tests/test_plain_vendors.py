@@ -260,3 +260,55 @@ def test_plain_vendors_gpu_parity():
     assert ",AMD_Instinct_" in amd["annotations"]["hami.io/amd-devices-allocated"]      # the device's type, not the key
     sample = next(r for (kind, arg), r in zip(ops, ref) if kind == "filter" and r["status"] == abi.HS_FIT and arg["containers"][0][0]["type"] == "Biren")
     assert "hami.io/Biren-devices-allocated" in sample["annotations"] and "hami.io/Biren-devices-to-allocate" in sample["annotations"]
+
+
+@pytest.mark.gpu
+def test_capacity_registered_nodes_gpu_parity():
+    """mthreads and cambricon nodes have no register annotation: their devices come from node capacity
+    (mthreads/device.go:130-153, cambricon/device.go:209-232).  Register those through HS_REG_CAPACITY_* and the
+    stream must decide exactly like the oracle fed with the derived device lists."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ingest_oracle as O
+    import k8s_vgpu_scheduler_b200.engine as eng
+    cfg, nodes, ops = _cluster(60, 900, seed=23)
+    mlu = []
+    for i, cards in enumerate((2, 8, 5)):                       # cambricon nodes: cores = 100 per card
+        name = "mlu-%02d" % i
+        devs = O.capacity_node_devices("MLU", name, cards * 100, cards * 96)
+        assert len(devs) == cards and devs[0]["Devmem"] == 24576
+        mlu.append((name, cards, {"name": name, "devices": [
+            {"id": d["ID"], "index": d["Index"], "count": d["Count"], "devmem": d["Devmem"], "devcore": d["Devcore"], "type": d["Type"],
+             "numa": 0, "mode": "", "health": True, "vendor": "MLU"} for d in devs]}))
+    nodes = nodes + [m[2] for m in mlu]
+    rng = random.Random(5)
+    for p in range(60):
+        uid = "mlu-pod-%03d" % p
+        req = {"key": "MLU", "type": "MLU", "nums": rng.choice([1, 1, 2]), "memreq": rng.choice([0, 4096, 24576]), "mempct": 0,
+               "coresreq": rng.choice([0, 25, 100])}
+        if req["memreq"] == 0:
+            req["mempct"] = 100
+        ops.insert(rng.randrange(len(ops)), ("filter", {"uid": uid, "ns": "default", "name": uid, "annotations": {}, "containers": [[req]], "n_init": 0}))
+    ref, ref_snap = parity.run_oracle(cfg, nodes, ops)
+    e = eng.Engine(cfg.get("node_policy"), cfg.get("gpu_policy"))
+    n_cap = 0
+    for n in nodes:
+        vendor = n["devices"][0]["vendor"]
+        nd = len(n["devices"])
+        if vendor == "Mthreads":
+            assert e.node_register(n["name"], [("Mthreads", abi.HS_REG_CAPACITY_MTHREADS, None, None, None, 16 * nd, 96 * nd)]) == nd, e.error()
+            n_cap += 1
+        elif vendor == "MLU":
+            assert e.node_register(n["name"], [("MLU", abi.HS_REG_CAPACITY_MLU, None, None, None, 100 * nd, 96 * nd)]) == nd, e.error()
+            n_cap += 1
+        else:
+            e.node_upsert(n)
+    assert n_cap >= 10
+    e.run_batch(eng.PackedOps(ops))
+    got = [e.batch_get(i) for i in range(len(ops))]
+    snap = {n["name"]: e.snapshot(n["name"]) for n in nodes}
+    assert e.node_register("mlu-zero", [("MLU", abi.HS_REG_CAPACITY_MLU, None, None, None, 0, 64)]) == 0 and "device not found" in e.error()
+    e.close()
+    assert parity.compare(ops, ref, got, ref_snap, snap) == []
+    fit_mlu = sum(1 for (k, a), r in zip(ops, ref) if k == "filter" and a["uid"].startswith("mlu-pod") and r["status"] == abi.HS_FIT)
+    assert fit_mlu > 20

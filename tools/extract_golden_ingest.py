@@ -104,11 +104,37 @@ def amd_fit_cases(ref):
     return out
 
 
+def capacity_node_cases(ref):
+    """cambricon / mthreads Test_GetNodeDevices: the node's capacity in, the derived DeviceInfo list out."""
+    out = []
+    for vendor, rel, fn, cores_res, mem_res in (
+            ("MLU", "pkg/device/cambricon/device_test.go", "Test_GetNodeDevices", "cambricon.com/mlu.smlu.vcore", "cambricon.com/mlu.smlu.vmemory"),
+            ("Mthreads", "pkg/device/mthreads/device_test.go", "Test_GetNodeDevices", "mthreads.com/sgpu-core", "mthreads.com/sgpu-memory")):
+        src = open(os.path.join(ref, rel)).read()
+        body = X.find_func(src, fn)
+        base = src[:src.index(body)].count("\n") + 1
+        for m in re.finditer(r'name:\s*"((?:[^"\\]|\\.)*)"', body):
+            blk = body[m.start():]
+            nxt = re.search(r'\n\t\t\},\n', blk)
+            blk = blk[:nxt.end()] if nxt else blk
+
+            def qty(res):
+                q = re.search(r'"%s":\s*\*resource\.NewQuantity\((-?\d+), resource\.DecimalSI\)' % re.escape(res), blk)
+                return int(q.group(1)) if q else 0
+            want = []
+            for w in re.finditer(r'Index:\s*(?:uint\()?(\d+)\)?,\s*ID:\s*"([^"]+)",\s*Count:\s*int32\((\d+)\),\s*Devmem:\s*int32\((\d+)\),\s*Devcore:\s*int32\((\d+)\)', blk):
+                want.append({"Index": int(w.group(1)), "ID": w.group(2), "Count": int(w.group(3)), "Devmem": int(w.group(4)),
+                             "Devcore": int(w.group(5)), "Type": vendor, "Numa": 0, "Health": True, "DeviceVendor": vendor})
+            out.append({"name": m.group(1), "source": "%s:%d" % (rel, base + body[:m.start()].count("\n")), "vendor": vendor,
+                        "node": re.search(r'Name:\s*"([^"]*)"', blk).group(1), "cores": qty(cores_res), "memory": qty(mem_res), "want": want})
+    return out
+
+
 def main():
     ref = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
     doc = {"note": "extracted from the reference's own tests by tools/extract_golden_ingest.py",
            "init_container": init_container_cases(ref), "nvidia_get_node_devices": pair_score_cases(ref),
-           "amd_fit": amd_fit_cases(ref)}
+           "amd_fit": amd_fit_cases(ref), "capacity_node_devices": capacity_node_cases(ref)}
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "ingest_funcs.json")
     with open(path, "w") as f:
         json.dump(doc, f, indent=1, sort_keys=True)
