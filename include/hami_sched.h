@@ -345,7 +345,13 @@ typedef struct hs_container_resources {
   const hs_quantity* limits;   uint32_t n_limits;     /* ctr.Resources.Limits   */
   const hs_quantity* requests; uint32_t n_requests;   /* ctr.Resources.Requests */
 } hs_container_resources;
-enum { HS_REQ_NVIDIA = 0, HS_REQ_DCU = 1, HS_REQ_MLU = 2, HS_REQ_ASCEND = 3 };
+enum { HS_REQ_NVIDIA = 0, HS_REQ_DCU = 1, HS_REQ_MLU = 2, HS_REQ_ASCEND = 3,
+       HS_REQ_ILUVATAR = 4,   /* iluvatar/device.go:201-254: memory_factor 256, cores default 0                  */
+       HS_REQ_COUNT = 5,      /* biren/device.go:141-165, vastai/device.go:143-167: the count only               */
+       HS_REQ_AMD = 6,        /* amd/device.go:217-266: Limits only; cores = percent of the card, default 100     */
+       HS_REQ_MTHREADS = 7,   /* mthreads/device.go:202-264: memory_factor 512; memory and cores divided by count */
+       HS_REQ_WHOLE_CARD = 8  /* enflame/gcu.go:91-111: Memreq 100, MemPercentagereq 100, Coresreq 100            */
+};
 typedef struct hs_vendor_resources {
   const char* common_word;             /* becomes the request's key and Type                                  */
   int32_t     kind;                    /* HS_REQ_*: whose GenerateResourceRequests                             */

@@ -2,6 +2,7 @@
 // (pkg/device/devices.go:639-691) over the vendors' GenerateResourceRequests:
 //   NVIDIA  pkg/device/nvidia/device.go:520-600     DCU     pkg/device/hygon/device.go:168-239
 //   MLU     pkg/device/cambricon/device.go:250-305  Ascend  pkg/device/ascend/device.go:303-378
+//   and the vendors of hs_config.vendors: iluvatar, biren / vastai, amd, mthreads, enflame GCU (cited at each case)
 // Input = the container's resource limits / requests with the three views of a resource.Quantity the reference
 // uses (AsInt64, Value, Sign), output = the ContainerDeviceRequest list hs_pod carries.  Plain host code.
 #include <stdint.h>
@@ -19,6 +20,13 @@ const hs_quantity* lookup(const hs_container_resources* c, const char* name) {
     if (c->limits[i].name && strcmp(c->limits[i].name, name) == 0) return &c->limits[i];
   for (uint32_t i = 0; i < c->n_requests; i++)
     if (c->requests[i].name && strcmp(c->requests[i].name, name) == 0) return &c->requests[i];
+  return nullptr;
+}
+
+const hs_quantity* lookup_limits(const hs_container_resources* c, const char* name) {
+  if (!name || !name[0]) return nullptr;
+  for (uint32_t i = 0; i < c->n_limits; i++)
+    if (c->limits[i].name && strcmp(c->limits[i].name, name) == 0) return &c->limits[i];
   return nullptr;
 }
 
@@ -93,6 +101,56 @@ bool generate(const hs_vendor_resources& v, const hs_container_resources* c, hs_
         corenum = (int32_t)core->value;
       }
       mempnum = memnum == 0 ? 100 : 0;
+      break;
+    }
+    case HS_REQ_ILUVATAR: {                                   // iluvatar/device.go:201-254 (MemoryFactor 256); no range check on n
+      if (mem) {
+        if (!mem->as_int64_ok || mem->as_int64 < 0 || mem->as_int64 > kMaxInt32 / factor) return false;
+        memnum = mem->as_int64 * factor;
+      }
+      corenum = 0;
+      if (core && core->as_int64_ok) corenum = (int32_t)core->as_int64;
+      mempnum = memnum == 0 ? 100 : 0;
+      break;
+    }
+    case HS_REQ_COUNT:                                        // biren/device.go:141-165, vastai/device.go:143-167
+      memnum = 0; mempnum = 100; corenum = 0;
+      break;
+    case HS_REQ_WHOLE_CARD:                                   // enflame/gcu.go:91-111
+      memnum = 100; mempnum = 100; corenum = 100;
+      break;
+    case HS_REQ_AMD: {                                        // amd/device.go:217-266: Limits only, Requests are ignored
+      cnt = lookup_limits(c, v.count_name);
+      if (!cnt || !cnt->as_int64_ok) return false;
+      if (cnt->as_int64 <= 0 || cnt->as_int64 > kMaxInt32) return false;
+      r.nums = (int32_t)cnt->as_int64;
+      mem = lookup_limits(c, v.memory_name);
+      if (mem) {
+        if (!mem->as_int64_ok || mem->as_int64 < 0 || mem->as_int64 > kMaxInt32) return false;
+        memnum = mem->as_int64;
+      }
+      corenum = 100;                                          // an omitted core limit = every CU of each card
+      core = lookup_limits(c, v.cores_name);
+      if (core) {
+        if (!core->as_int64_ok || core->as_int64 < 1 || core->as_int64 > 100) return false;
+        corenum = (int32_t)core->as_int64;
+      }
+      mempnum = 0;
+      r.key = v.common_word; r.type = v.common_word;
+      r.memreq = (int32_t)memnum; r.mempct = mempnum; r.coresreq = corenum;
+      return true;
+    }
+    case HS_REQ_MTHREADS: {                                   // mthreads/device.go:202-264 (MemoryFactor 512): per-card shares
+      if (n <= 0 || n > kMaxInt32) return false;
+      if (mem) {
+        if (!mem->as_int64_ok || mem->as_int64 < 0 || mem->as_int64 > kMaxInt32 / factor) return false;
+        memnum = mem->as_int64 * factor;
+      }
+      corenum = 0;
+      if (core && core->as_int64_ok) corenum = (int32_t)core->as_int64;
+      mempnum = memnum == 0 ? 100 : 0;
+      memnum = (int32_t)memnum / (int32_t)n;                  // Memreq: int32(memnum) / int32(n)
+      corenum = corenum / (int32_t)n;
       break;
     }
     default:

@@ -117,6 +117,43 @@ def oracle_generate(v, limits, requests):
         if core is not None and core[1]:
             cores = wrap(core[0])
         pctn = 100 if memnum == 0 else 0
+    elif v["kind"] == abi.HS_REQ_ILUVATAR:       # iluvatar/device.go:201-254
+        if mem is not None:
+            if not mem[1] or mem[0] < 0 or mem[0] > MAXI32 // factor:
+                return None
+            memnum = mem[0] * factor
+        cores = wrap(core[0]) if core is not None and core[1] else 0
+        pctn = 100 if memnum == 0 else 0
+    elif v["kind"] == abi.HS_REQ_COUNT:          # biren/device.go:141-165, vastai/device.go:143-167
+        memnum, pctn, cores = 0, 100, 0
+    elif v["kind"] == abi.HS_REQ_WHOLE_CARD:     # enflame/gcu.go:91-111
+        memnum, pctn, cores = 100, 100, 100
+    elif v["kind"] == abi.HS_REQ_AMD:            # amd/device.go:217-266: Limits only
+        cnt, mem, core = limits.get(v["count"]), limits.get(v["mem"]), limits.get(v["cores"])
+        if cnt is None or not cnt[1] or cnt[0] <= 0 or cnt[0] > MAXI32:
+            return None
+        n = cnt[0]
+        if mem is not None:
+            if not mem[1] or mem[0] < 0 or mem[0] > MAXI32:
+                return None
+            memnum = mem[0]
+        cores = 100
+        if core is not None:
+            if not core[1] or core[0] < 1 or core[0] > 100:
+                return None
+            cores = core[0]
+        pctn = 0
+    elif v["kind"] == abi.HS_REQ_MTHREADS:       # mthreads/device.go:202-264
+        if n <= 0 or n > MAXI32:
+            return None
+        if mem is not None:
+            if not mem[1] or mem[0] < 0 or mem[0] > MAXI32 // factor:
+                return None
+            memnum = mem[0] * factor
+        cores = wrap(core[0]) if core is not None and core[1] else 0
+        pctn = 100 if memnum == 0 else 0
+        godiv = lambda a, b: abs(a) // abs(b) * (1 if (a < 0) == (b < 0) else -1)   # noqa: E731
+        memnum, cores = godiv(memnum, n), godiv(cores, n)
     else:
         if n <= 0 or n > MAXI32:
             return None
@@ -178,9 +215,22 @@ def strip(r):
     return None if r is None else {k: r[k] for k in ("Nums", "Type", "Memreq", "MemPercentagereq", "Coresreq")}
 
 
+def _plain(word, kind, count, mem=None, cores=None, factor=1):
+    return dict(word=word, kind=kind, count=count, mem=mem, pct=None, cores=cores, default_mem=0, default_cores=0, factor=factor)
+
+
+ILUVATAR = _plain("MR-V100", abi.HS_REQ_ILUVATAR, "iluvatar.ai/MR-V100-vgpu", "iluvatar.ai/MR-V100.vMem", "iluvatar.ai/MR-V100.vCore", 256)
+BIREN = _plain("Biren", abi.HS_REQ_COUNT, "birentech.com/gpu")
+VASTAI = _plain("Vastai", abi.HS_REQ_COUNT, "vastaitech.com/va")
+MTHREADS = _plain("Mthreads", abi.HS_REQ_MTHREADS, "mthreads.com/vgpu", "mthreads.com/sgpu-memory", "mthreads.com/sgpu-core", 512)
+GCU = _plain("GCU", abi.HS_REQ_WHOLE_CARD, "enflame.com/gcu")
+AMD = _plain("AMD", abi.HS_REQ_AMD, "amd.com/gpu", "amd.com/gpu-mem", "amd.com/gpu-core-pct")
+
 TABLES = [("nvidia_generate_requests", NVIDIA, 15), ("hygon_generate_requests", DCU, 5), ("hygon_generate_requests_range", DCU, 2),
           ("cambricon_generate_requests", MLU, 6), ("ascend_generate_requests", ASCEND_910A, 3),
-          ("ascend_generate_requests_range", ASCEND_CORE, 7)]
+          ("ascend_generate_requests_range", ASCEND_CORE, 7),
+          ("iluvatar_generate_requests", ILUVATAR, 5), ("biren_generate_requests", BIREN, 4), ("vastai_generate_requests", VASTAI, 4),
+          ("mthreads_generate_requests", MTHREADS, 8), ("gcu_generate_requests", GCU, 3)]
 
 
 @pytest.mark.parametrize("name,vendor,count", TABLES, ids=[t[0] for t in TABLES])
@@ -220,10 +270,28 @@ def test_resourcereqs_keeps_only_positive_counts_in_vendor_order():
     assert [g["Type"] for g in got] == ["NVIDIA", "MLU"] and got[1]["Memreq"] == 2560
 
 
+def test_amd_generate_requests_golden():
+    """amd/device_test.go Test_GenerateResourceRequests (t.Run blocks + loop table → ingest_funcs.json): Limits only."""
+    cases = json.load(open(os.path.join(ROOT, "tests", "golden", "ingest_funcs.json")))["amd_generate_requests"]
+    assert len(cases) == 9
+    q = lambda d: {k: quantity(v) for k, v in d.items()}   # noqa: E731
+    for c in cases:
+        limits, requests = q(c["limits"]), q(c["requests"])
+        ref = oracle_generate(AMD, limits, requests)
+        got = product_generate([AMD], limits, requests)
+        got = strip(got[0]) if got else None
+        assert strip(ref) == got, c["name"]
+        if "want_partial" in c:
+            assert all(got[k] == v for k, v in c["want_partial"].items()), c["name"]
+        else:
+            assert got == c["want"], c["name"]
+
+
 def test_product_matches_restatement_on_random_containers():
     rng = random.Random(42)
     vendors = [NVIDIA, dict(NVIDIA, word="NV2", factor=4, default_mem=777, default_cores=5), DCU, dict(DCU, word="DCU2", factor=3),
-               MLU, ASCEND_910A, ASCEND_CORE, dict(ASCEND_CORE, word="AscF", factor=2)]
+               MLU, ASCEND_910A, ASCEND_CORE, dict(ASCEND_CORE, word="AscF", factor=2),
+               ILUVATAR, BIREN, MTHREADS, GCU, AMD]
     names = sorted({v[k] for v in vendors for k in ("count", "mem", "pct", "cores") if v[k]})
     pool = [0, 1, 2, 8, -1, -100, 100, 101, 150, 4096, 2 ** 31 - 1, 2 ** 31, 2200000000, 2 ** 32 + 50, 8388607, 8388608,
             {"_quantity": "16Gi"}, {"_quantity": "16.0Gi"}, {"_quantity": "-1m"}, {"_quantity": "1500m"}, {"_quantity": "2000m"}]

@@ -446,6 +446,12 @@ TABLES = [
     ("cambricon_generate_requests", "pkg/device/cambricon/device_test.go", "Test_GenerateResourceRequests", "tests"),
     ("ascend_generate_requests", "pkg/device/ascend/device_test.go", "Test_GenerateResourceRequests", "tests"),
     ("ascend_generate_requests_range", "pkg/device/ascend/device_test.go", "Test_GenerateResourceRequests_OutOfRangeValues", "tests"),
+    ("iluvatar_generate_requests", "pkg/device/iluvatar/device_test.go", "Test_GenerateResourceRequests", "tests"),
+    ("biren_generate_requests", "pkg/device/biren/device_test.go", "Test_GenerateResourceRequests", "tests"),
+    ("amd_generate_requests", "pkg/device/amd/device_test.go", "Test_GenerateResourceRequests", "tests"),
+    ("mthreads_generate_requests", "pkg/device/mthreads/device_test.go", "Test_GenerateResourceRequests", "tests"),
+    ("vastai_generate_requests", "pkg/device/vastai/device_test.go", "Test_GenerateResourceRequests", "tests"),
+    ("gcu_generate_requests", "pkg/device/enflame/gcu_test.go", "TestGCUDevices_GenerateResourceRequests", "tests"),
     ("iluvatar_fit", "pkg/device/iluvatar/device_test.go", "Test_Fit", "tests"),
     ("biren_fit", "pkg/device/biren/device_test.go", "TestDevices_Fit", "tests"),
     ("mthreads_fit", "pkg/device/mthreads/device_test.go", "TestDevices_Fit", "tests"),

@@ -104,6 +104,44 @@ def amd_fit_cases(ref):
     return out
 
 
+def amd_request_cases(ref):
+    """pkg/device/amd/device_test.go Test_GenerateResourceRequests: three t.Run blocks and one loop table."""
+    rel = "pkg/device/amd/device_test.go"
+    src = open(os.path.join(ref, rel)).read()
+    body = X.find_func(src, "Test_GenerateResourceRequests")
+    base = src[:src.index(body)].count("\n") + 1
+    num = lambda s: int(eval(s.replace("math.MaxInt32", "2147483647"), {"__builtins__": {}}))   # noqa: E731
+    qty = r'"([^"]+)":\s*\*resource\.NewQuantity\(([^,]+), resource\.DecimalSI\)'
+    out = []
+    loop_at = body.index("for _, tc := range")
+    starts = [m.start() for m in re.finditer(r'\bt\.Run\("', body[:loop_at])] + [loop_at]
+    for a, b in zip(starts, starts[1:]):
+        blk = body[a:b]
+        name = re.match(r't\.Run\("((?:[^"\\]|\\.)*)"', blk).group(1)
+        lim_at, req_at = blk.find("Limits:"), blk.find("Requests:")
+        lim_txt = blk[lim_at:req_at] if req_at > lim_at >= 0 else blk[lim_at:]
+        req_txt = blk[req_at:] if req_at >= 0 else ""
+        case = {"name": name, "source": "%s:%d" % (rel, base + body[:a].count("\n")),
+                "limits": {k: num(v) for k, v in re.findall(qty, lim_txt)}, "requests": {k: num(v) for k, v in re.findall(qty, req_txt)}}
+        full = re.search(r"Nums:\s*(\d+),\s*Type:\s*AMDDevice,\s*Memreq:\s*(\d+),\s*MemPercentagereq:\s*(\d+),\s*Coresreq:\s*(\d+)", blk)
+        part = re.search(r"assert\.Equal\(t, int32\((\d+)\), got\.Coresreq\)", blk)
+        if full:
+            case["want"] = {"Nums": int(full.group(1)), "Type": "AMD", "Memreq": int(full.group(2)),
+                            "MemPercentagereq": int(full.group(3)), "Coresreq": int(full.group(4))}
+        elif part:
+            case["want_partial"] = {"Coresreq": int(part.group(1))}
+        else:
+            assert "device.ContainerDeviceRequest{}, got" in blk, name
+            case["want"] = None
+        out.append(case)
+    loop = body[loop_at:]
+    base_limits = {k: num(v) for k, v in re.findall(qty, loop)}
+    for m in re.finditer(r'\{name:\s*"([^"]+)",\s*resource:\s*"([^"]+)",\s*value:\s*([^}]+)\}', loop):
+        out.append({"name": m.group(1), "source": "%s:%d" % (rel, base + body[:loop_at + m.start()].count("\n")),
+                    "limits": dict(base_limits, **{m.group(2): num(m.group(3))}), "requests": {}, "want": None})
+    return out
+
+
 def capacity_node_cases(ref):
     """cambricon / mthreads Test_GetNodeDevices: the node's capacity in, the derived DeviceInfo list out."""
     out = []
@@ -134,7 +172,8 @@ def main():
     ref = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
     doc = {"note": "extracted from the reference's own tests by tools/extract_golden_ingest.py",
            "init_container": init_container_cases(ref), "nvidia_get_node_devices": pair_score_cases(ref),
-           "amd_fit": amd_fit_cases(ref), "capacity_node_devices": capacity_node_cases(ref)}
+           "amd_fit": amd_fit_cases(ref), "capacity_node_devices": capacity_node_cases(ref),
+           "amd_generate_requests": amd_request_cases(ref)}
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "ingest_funcs.json")
     with open(path, "w") as f:
         json.dump(doc, f, indent=1, sort_keys=True)
