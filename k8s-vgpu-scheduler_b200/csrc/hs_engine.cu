@@ -957,7 +957,7 @@ int run_device_ops_sharded(hs_handle* h, int n_ops, size_t n_entries, size_t n_u
     const DevPod& p = h->b_pods.h[op];
     cudaError_t le = cudaSuccess;
     if (p.op == OP_FILTER) {
-      const int mode = !p.fast ? 0 : (((p.flags & PF_NUMA_ASSERT) && p.e0.vendor == HV_NVIDIA) ? 1 : 2);
+      const int mode = !p.fast ? 0 : (hs_verdict_needs_order(p) ? 1 : 2);
       const int grid = std::max(1, std::min(sms * hs_sweep_blocks_per_sm(mode), (n_nodes * HS_D + block - 1) / block));
       le = (cudaError_t)hs_launch_sweep(&ka, op, mode, grid, block, h->stream);
       if (le == cudaSuccess && h->shard_world > 1) {
@@ -1961,7 +1961,7 @@ int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* 
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
   const int block = 256;
-  const int mode = !c.pod.fast ? 0 : (((c.pod.flags & PF_NUMA_ASSERT) && c.pod.e0.vendor == HV_NVIDIA) ? 1 : 2);
+  const int mode = !c.pod.fast ? 0 : (hs_verdict_needs_order(c.pod) ? 1 : 2);
   const int grid = std::max(1, std::min(sms * hs_sweep_blocks_per_sm(mode), (ka.n_nodes * HS_D + block - 1) / block));   // one resident wave
   cudaError_t le = (cudaError_t)hs_launch_sweep(&ka, 0, mode, grid, block, h->stream);   // warm-up
   if (le != cudaSuccess) { h->err = cudaGetErrorString(le); return HS_ERR_CUDA; }
@@ -2139,7 +2139,7 @@ hs_sweep_static_kernel(const int4* __restrict__ dyn, const int4* __restrict__ st
   const int lane = threadIdx.x & 31, glane = lane & 7, gbase = lane & 24;
   const int gg = gtid >> 3, ngroups = (gridDim.x * blockDim.x) >> 3;
   const bool spread = pod.flags & PF_NODE_SPREAD;
-  const bool lite = !((pod.flags & PF_NUMA_ASSERT) && pod.e0.vendor == HV_NVIDIA);
+  const bool lite = !hs_verdict_needs_order(pod);
   unsigned long long my_key = 0;
   DevRegs n;
   FastEval fe;

@@ -373,7 +373,7 @@ hs_decide_kernel(const KernelArgs ka) {
     // Without numa-bind the VERDICT needs no score/sort (fast_fit_lite).  Streaming mode: the winner's warp runs the
     // full evaluation afterwards.  Resident mode on one GPU: every group that fits runs it while the barrier's
     // arrivals are in flight (`deferred`), so the winner still commits straight after the barrier.
-    const bool lite = fast && !((pod.flags & PF_NUMA_ASSERT) && pod.e0.vendor == HV_NVIDIA) && (!resident || ka.world <= 1);
+    const bool lite = fast && !hs_verdict_needs_order(pod) && (!resident || ka.world <= 1);
     const bool deferred = lite && resident;
     const DevEntry* ent = &pod.e0;
     if (pod.n_entries > 1) {     // general path with several entries: fetch them from the pool

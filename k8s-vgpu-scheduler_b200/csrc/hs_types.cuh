@@ -107,6 +107,22 @@ static_assert(sizeof(RelDelta) * HS_D == 64, "RelDelta rows overlay DevPod::e0")
 static_assert(sizeof(DevEntry) == 64, "DevEntry layout");
 static_assert(sizeof(DevPod) == 160, "DevPod layout: 96 B header + 64 B first entry, 16 B chunks for cp.async");
 
+// numa-bind (nvidia/device.go:770-777) restarts Fit's collection whenever the NUMA id changes along the sorted list.
+// With numa-bind the comparator is numa-major for every policy but "mutex" (policy/gpu_policy.go:101-112,139-147), so
+// each NUMA id is ONE run and the verdict does not depend on the order inside it; only under "mutex" (sorted by Used)
+// does the verdict need the real order.
+#if defined(__CUDACC__)
+#define HS_HD __host__ __device__
+#else
+#define HS_HD
+#endif
+HS_HD inline bool hs_numa_major(const DevPod& p) {
+  return p.sort_mode == SORT_NUMA_BINPACK || p.sort_mode == SORT_NUMA_SPREAD || (p.sort_mode == SORT_CHAIN && p.chain[0] == CK_NUMA);
+}
+HS_HD inline bool hs_verdict_needs_order(const DevPod& p) {
+  return (p.flags & PF_NUMA_ASSERT) && p.e0.vendor == HV_NVIDIA && !hs_numa_major(p);
+}
+
 struct DevAlloc {           // one ContainerDevice, 8 B
   uint8_t entry;            // index into the pod's entries (container + type)
   uint8_t dev;              // device slot on the node

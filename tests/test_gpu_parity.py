@@ -193,3 +193,45 @@ def test_sharded_pipeline_single_rank(name, kw, monkeypatch):
     monkeypatch.setenv("HS_FORCE_SHARD", "1")
     cfg, nodes, ops = _gen().CONFIGS[name](**kw)
     _check(cfg, nodes, ops)
+
+
+def test_numa_bind_verdict_without_the_sort():
+    """numa-bind pods on the register-resident path: the verdict comes from per-NUMA counts whenever the comparator
+    is numa-major (policy/gpu_policy.go:101-112,139-147) and from the real order under "mutex".  Random NUMA layouts
+    (ids 0-3, not contiguous in registration order), unhealthy devices, every device policy, with and without
+    topology-aware, nums 1-4 — decisions, picks and reasons equal to the oracle's."""
+    import random
+    rng = random.Random(314)
+    nodes = []
+    for i in range(320):
+        nd = rng.randrange(2, 9)
+        devs = []
+        for d in range(nd):
+            devs.append({"id": "GPU-nb%03d-%d" % (i, d), "index": d, "count": rng.choice([2, 4, 10]), "devmem": 81920, "devcore": 100,
+                         "type": "NVIDIA A100-SXM4-80GB", "numa": rng.randrange(0, 4) if i % 3 else d // 4, "mode": "hami-core",
+                         "health": rng.random() > 0.08, "vendor": "NVIDIA"})
+        node = {"name": "nb-%03d" % i, "devices": devs}
+        if i % 5 == 0:
+            node["pair_scores"] = [[0 if a == b else rng.choice([10, 20, 40, 60]) for b in range(nd)] for a in range(nd)]
+        nodes.append(node)
+    policies = ["binpack", "spread", "mutex", "topology-aware", "binpack,numa", "numa", "spread,numa", "numa,binpack",
+                "mutex,topology-aware", "binpack,topology-aware", "topology-aware,spread"]
+    ops, live = [], []
+    for p in range(2500):
+        uid = "nb-%05d" % p
+        annos = {"nvidia.com/numa-bind": rng.choice(["true", "true", "true", "1", "false"])}
+        if rng.random() < 0.85:
+            annos["hami.io/gpu-scheduler-policy"] = rng.choice(policies)
+        if rng.random() < 0.5:
+            annos["hami.io/node-scheduler-policy"] = rng.choice(["binpack", "spread"])
+        req = {"key": "NVIDIA", "type": "NVIDIA", "nums": rng.choice([1, 1, 2, 2, 3, 4]), "memreq": rng.choice([0, 8192, 30000, 60000]),
+               "mempct": 101, "coresreq": rng.choice([0, 20, 50, 100])}
+        if req["memreq"] == 0:
+            req["mempct"] = rng.choice([25, 50, 100])
+        ops.append(("filter", {"uid": uid, "ns": "default", "name": uid, "annotations": annos, "containers": [[req]], "n_init": 0}))
+        live.append(uid)
+        while len(live) > 900:
+            ops.append(("delete", live.pop(rng.randrange(len(live)))))
+    ref = _check({"node_policy": "binpack", "gpu_policy": "spread"}, nodes, ops, chunk=700)
+    st = [r["status"] for (k, _), r in zip(ops, ref) if k == "filter"]
+    assert st.count(abi.HS_FIT) > 800 and st.count(abi.HS_NOFIT) > 100
