@@ -98,6 +98,10 @@ typedef struct hs_node_info {
   const int32_t*        pair_scores;
   const char*           device_cordon;  /* annotation hami.io/device-cordon (nvidia/device.go:59), NULL = absent */
   int8_t                hami_vnpu_core; /* annotation hami-vnpu-core: -1 absent, 1 == "true", 0 any other value (ascend/device.go:463-467) */
+  /* annotations metax-tech.com/gpu.topology.losses / .scores (metax/device.go:38-39,185-214): JSON {"<devices>": value};
+   * NULL = absent.  Read by the HS_FIT_METAX vendor's ScoreNode; such a node must hold that vendor's devices only. */
+  const char*           metax_losses;
+  const char*           metax_scores;
 } hs_node_info;
 
 /* ---- pod --------------------------------------------------------------- */
@@ -223,7 +227,12 @@ enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
        HS_FIT_MTHREADS = 3,
        /* enflame GCU, whole cards (pkg/device/enflame/gcu.go:144-183): health, type, and a card in use at all is an
         * "ExclusiveDeviceAllocateConflict"; no uuid lists, no slot count; the pick records Memreq and Coresreq as asked */
-       HS_FIT_WHOLE_CARD = 4 };
+       HS_FIT_WHOLE_CARD = 4,
+       /* metax whole GPUs, "Metax-GPU" (pkg/device/metax/device.go:223-334): the template gates without uuid lists
+        * (checkUUID is constant true) plus mthreads' customFilterRule; plain PatchAnnotations (:91-103); ScoreNode
+        * (:185-214) adds 2000 - losses[n] under node policy "binpack" and 2000 - scores[n] under "spread", n = the
+        * devices the pod received, from hs_node_info.metax_losses / metax_scores                                    */
+       HS_FIT_METAX = 5 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */
@@ -350,7 +359,8 @@ enum { HS_REQ_NVIDIA = 0, HS_REQ_DCU = 1, HS_REQ_MLU = 2, HS_REQ_ASCEND = 3,
        HS_REQ_COUNT = 5,      /* biren/device.go:141-165, vastai/device.go:143-167: the count only               */
        HS_REQ_AMD = 6,        /* amd/device.go:217-266: Limits only; cores = percent of the card, default 100     */
        HS_REQ_MTHREADS = 7,   /* mthreads/device.go:202-264: memory_factor 512; memory and cores divided by count */
-       HS_REQ_WHOLE_CARD = 8  /* enflame/gcu.go:91-111: Memreq 100, MemPercentagereq 100, Coresreq 100            */
+       HS_REQ_WHOLE_CARD = 8, /* enflame/gcu.go:91-111: Memreq 100, MemPercentagereq 100, Coresreq 100            */
+       HS_REQ_METAX = 9       /* metax/device.go:134-154: Memreq 0, MemPercentagereq 100, Coresreq 100            */
 };
 typedef struct hs_vendor_resources {
   const char* common_word;             /* becomes the request's key and Type                                  */
@@ -376,7 +386,10 @@ enum { HS_REG_CSV = 0,    /* device.DecodeNodeDevices  (pkg/device/devices.go:31
        /* no annotation at all: the devices are derived from the node's CAPACITY (capacity_cores / capacity_memory =
         * AsInt64 of Status.Capacity[<cores resource>] / [<memory resource>]) and named after the node:               */
        HS_REG_CAPACITY_MLU = 2,      /* cambricon/device.go:209-232: one card per 100 cores, <node>-cambricon-mlu-<i>   */
-       HS_REG_CAPACITY_MTHREADS = 3  /* mthreads/device.go:130-153: one card per 16 cores, <node>-mthreads-<i>          */
+       HS_REG_CAPACITY_MTHREADS = 3, /* mthreads/device.go:130-153: one card per 16 cores, <node>-mthreads-<i>          */
+       HS_REG_CAPACITY_METAX = 4     /* metax/device.go:67-89: capacity_cores = the GPU count, <node>-metax-<i>, Count 1;
+                                      * `annotation` / `pair_scores` = the node's metax-tech.com/gpu.topology.losses /
+                                      * .scores values or NULL (hs_node_register hands them to hs_node_info)            */
 };
 
 typedef struct hs_vendor_registration {

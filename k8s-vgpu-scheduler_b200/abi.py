@@ -26,7 +26,8 @@ class hs_device_info(C.Structure):
 
 class hs_node_info(C.Structure):
     _fields_ = [("name", C.c_char_p), ("devices", C.POINTER(hs_device_info)), ("n_devices", C.c_uint32),
-                ("pair_scores", C.POINTER(C.c_int32)), ("device_cordon", C.c_char_p), ("hami_vnpu_core", C.c_int8)]
+                ("pair_scores", C.POINTER(C.c_int32)), ("device_cordon", C.c_char_p), ("hami_vnpu_core", C.c_int8),
+                ("metax_losses", C.c_char_p), ("metax_scores", C.c_char_p)]
 
 
 class hs_vendor_registration(C.Structure):
@@ -44,7 +45,7 @@ class hs_sim_node(C.Structure):
                 ("device_cordon", C.c_char_p), ("hami_vnpu_core", C.c_int8)]
 
 
-HS_REG_CSV, HS_REG_JSON, HS_REG_CAPACITY_MLU, HS_REG_CAPACITY_MTHREADS = 0, 1, 2, 3
+HS_REG_CSV, HS_REG_JSON, HS_REG_CAPACITY_MLU, HS_REG_CAPACITY_MTHREADS, HS_REG_CAPACITY_METAX = 0, 1, 2, 3, 4
 
 
 class hs_container_request(C.Structure):
@@ -110,7 +111,7 @@ class hs_vendor_resources(C.Structure):
 
 
 HS_REQ_NVIDIA, HS_REQ_DCU, HS_REQ_MLU, HS_REQ_ASCEND = 0, 1, 2, 3
-HS_REQ_ILUVATAR, HS_REQ_COUNT, HS_REQ_AMD, HS_REQ_MTHREADS, HS_REQ_WHOLE_CARD = 4, 5, 6, 7, 8
+HS_REQ_ILUVATAR, HS_REQ_COUNT, HS_REQ_AMD, HS_REQ_MTHREADS, HS_REQ_WHOLE_CARD, HS_REQ_METAX = 4, 5, 6, 7, 8, 9
 
 
 class hs_vendor_config(C.Structure):
@@ -119,7 +120,7 @@ class hs_vendor_config(C.Structure):
                 ("use_type_key", C.c_char_p), ("nouse_type_key", C.c_char_p)]
 
 
-HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD = 0, 1, 2, 3, 4
+HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD, HS_FIT_METAX = 0, 1, 2, 3, 4, 5
 
 # The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
 # (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
@@ -139,6 +140,8 @@ DEFAULT_VENDORS = [
     # mthreads/device.go:44-58,76-80
     ("Mthreads", HS_FIT_MTHREADS, "mthreads.ai/use-gpuuuid", "mthreads.ai/nouse-gpuuuid",
      "hami.io/mthreads-vgpu-devices-to-allocate", "hami.io/mthreads-vgpu-devices-allocated"),
+    # metax whole GPUs (metax/device.go:35-56): no uuid lists
+    ("Metax-GPU", HS_FIT_METAX, None, None, "hami.io/metax-gpu-devices-to-allocate", "hami.io/metax-gpu-devices-allocated"),
 ]
 
 
@@ -221,7 +224,7 @@ def build_node(node):
         ps = C.cast(flat, C.POINTER(C.c_int32))
         keep.append(flat)
     ni = hs_node_info(_b(node["name"]), arr, len(devs), ps, _b(node.get("device_cordon")),
-                      node.get("hami_vnpu_core", -1))
+                      node.get("hami_vnpu_core", -1), _b(node.get("metax_losses")), _b(node.get("metax_scores")))
     return ni, keep
 
 

@@ -140,6 +140,7 @@ struct VendorInfo {
   bool count_only = false;  // biren's Fit: no memory / core gates (EF_COUNT_ONLY)
   bool whole_card = false;  // enflame GCU's Fit: a card in use at all is a conflict (EF_WHOLE_CARD)
   bool mthreads = false;    // mthreads' Fit: template gates + customFilterRule; its own annotation set (EF_MTHREADS)
+  bool metax = false;       // metax whole GPUs: mthreads' gates without uuid lists + ScoreNode from the node's annotations (EF_METAX)
   bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
 };
@@ -581,6 +582,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
   p.op = OP_FILTER;
   p.w_slot = (float)w[0]; p.w_core = (float)w[1]; p.w_mem = (float)w[2];
   if (nodePolicy == "spread") p.flags |= PF_NODE_SPREAD;
+  if (nodePolicy == "binpack") p.flags |= PF_NODE_BINPACK;
   if (policyContains(gpuPolicy, "mutex")) p.flags |= PF_MUTEX;
   if (policyContains(gpuPolicy, "topology-aware")) p.flags |= PF_TOPOLOGY;
   if (numaBind) p.flags |= PF_NUMA_ASSERT;
@@ -637,7 +639,8 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       e.vendor = v ? (uint16_t)v->gate : (uint16_t)HV_NONE;
       if (v && v->count_only) e.flags |= EF_COUNT_ONLY;
       if (v && v->amd) e.flags |= EF_AMD;
-      if (v && v->mthreads) e.flags |= EF_MTHREADS;
+      if (v && (v->mthreads || v->metax)) e.flags |= EF_MTHREADS;   // metax/device.go:156-166 is mthreads' customFilterRule
+      if (v && v->metax) e.flags |= EF_METAX;
       if (v && v->whole_card) e.flags |= EF_WHOLE_CARD;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
@@ -656,7 +659,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
           if (!uuid_words(h, list, uuid_pool, e.nouse_off, e.nouse_cnt)) { h->err = "no-use-uuid list spans too many nodes"; return HS_ERR_UNSUPPORTED; }
       }
       keyset.insert(ktype);
-      if (v && v->ascend910) slotset.insert(ktype);
+      if (v && (v->ascend910 || v->metax)) slotset.insert(ktype);   // vendors whose ScoreNode is not constant 0
       c.entries.push_back(e);
       c.meta.entries.push_back(EntryMeta{ktype, (int)ci, v ? v->id : -1});
       int nn = q->nums < 0 ? 0 : (q->nums > HS_D ? HS_D : q->nums);
@@ -679,7 +682,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     const DevEntry& e = c.entries[0];
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
               !(e.flags & EF_ASCEND910)) ? 1 : 0;
-    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD))) p.fast = 0;
+    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX))) p.fast = 0;
   }
   quota_rows_for(h, c.meta.ns, p);
   if (p.q_idx[0] >= 0 || p.q_idx[1] >= 0) p.fast = 0;   // the quota check lives in the general evaluator (hs_eval.cuh)
@@ -1535,6 +1538,8 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.amd = vc.fit_kind == HS_FIT_AMD;
       v.mthreads = vc.fit_kind == HS_FIT_MTHREADS;
       v.whole_card = vc.fit_kind == HS_FIT_WHOLE_CARD;
+      v.metax = vc.fit_kind == HS_FIT_METAX;
+      if (v.metax) { v.use_uuid.clear(); v.nouse_uuid.clear(); }   // checkUUID is constant true (metax/device.go:124-126)
       if (vc.use_type_key) v.use_type = vc.use_type_key;
       if (vc.nouse_type_key) v.nouse_type = vc.nouse_type_key;
       if (vc.use_uuid_key) v.use_uuid = vc.use_uuid_key;
@@ -1699,6 +1704,26 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
       if (i != j) { if (!have) { have = true; uval = v; } else if (v != uval) uniform = false; }
     }
   uint32_t nf = (uint32_t)n | NF_ALIVE | (uniform ? NF_PAIR_UNIFORM : 0u);
+  {   // metax ScoreNode tables (metax/device.go:168-214): values for 0..31 devices ride in the node's pair tile
+    int n_metax = 0;
+    for (const auto& d : ns.devs) if (d.vendor_id != HV_NONE && h->vendors[d.vendor_id].metax) n_metax++;
+    if (n_metax > 0 && (node->metax_losses || node->metax_scores)) {
+      if (n_metax != n) { h->err = "a node with metax topology annotations must hold metax devices only (the engine's pair tile carries the tables)"; return HS_ERR_UNSUPPORTED; }
+      for (int which = 0; which < 2; which++) {
+        const char* text = which == 0 ? node->metax_losses : node->metax_scores;
+        if (!text) continue;
+        nf |= which == 0 ? NF_METAX_LOSS : NF_METAX_SCORE;
+        std::vector<std::pair<int64_t, int64_t>> m;
+        if (!hs_ingest::decode_int_map(text, m)) continue;          // any error: every lookup reads 0
+        for (auto& kv : m) {
+          if (kv.second == 0) continue;
+          if (kv.first < 0) continue;                                // a device count is never negative
+          if (kv.first > 31 || kv.second > 32767 || kv.second < -32768) { h->err = "metax topology table outside the engine's range (counts 0..31, int16 values)"; return HS_ERR_UNSUPPORTED; }
+          P[which * 32 + (int)kv.first] = (int16_t)kv.second;
+        }
+      }
+    }
+  }
   bool vnpu = h->ascend_vnpu_default;
   if (ns.vnpu >= 0) vnpu = ns.vnpu == 1;
   if (vnpu) nf |= NF_VNPU_CORE;

@@ -521,7 +521,7 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
         a.usedmem = fc.tmp_mem[t];
         out.allocs[out.n_alloc++] = a;
       }
-      if (e.score_slot >= 0) {
+      if (e.score_slot >= 0 && !(e.flags & EF_METAX)) {
         const int net = (int)DF_NET(w.dflags[d]);
         if (net == 255) missing_net = true;
         int c = 0;
@@ -530,7 +530,10 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
       }
     }
     // Ascend ScoreNode per container, ascend/device.go:388-424
-    if (e.score_slot >= 0 && fc.ntmp > 0) {
+    if (e.score_slot >= 0 && (e.flags & EF_METAX)) {
+      // metax ScoreNode (metax/device.go:185-214) only counts the pod's devices: the slot's accumulator is that count
+      score_acc[e.score_slot] = __fadd_rn(score_acc[e.score_slot], (float)fc.ntmp);
+    } else if (e.score_slot >= 0 && fc.ntmp > 0) {
       if (missing_net) *score_zero |= 1u << e.score_slot;
       else score_acc[e.score_slot] = __fadd_rn(score_acc[e.score_slot], __fdiv_rn((float)netcnt_max, (float)fc.ntmp));
     }
@@ -554,6 +557,9 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   if (ka.quota != nullptr && (pod.q_idx[0] >= 0 || pod.q_idx[1] >= 0)) { quota_load(qacc, pod, ka); qa = &qacc; }
   const bool base_key[2] = {(nflags & NF_BASE_NV) != 0, (nflags & NF_BASE_MLU) != 0};
   w.mth_prev = 0;
+  uint32_t metax_slots = 0;           // score slots that belong to a metax type (their accumulator is a device count)
+  for (int e = 0; e < pod.n_entries; e++)
+    if ((ent[e].flags & EF_METAX) && ent[e].score_slot >= 0) metax_slots |= 1u << ent[e].score_slot;
 
   if (pod.n_init > 0) {
     int bu[HS_D], bm[HS_D], bc[HS_D];
@@ -591,7 +597,15 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   float devScore = 0.0f;
 #pragma unroll
   for (int s = 0; s < HS_SCORE_SLOTS; s++) {
-    const float v = ((score_zero >> s) & 1u) ? 0.0f : __fmul_rn(score_acc[s], 10.0f);
+    float v = ((score_zero >> s) & 1u) ? 0.0f : __fmul_rn(score_acc[s], 10.0f);
+    if ((metax_slots >> s) & 1u) {
+      // 2000 - losses[n] under node policy "binpack", 2000 - scores[n] under "spread", 0 without the annotation
+      const int cnt = (int)score_acc[s];
+      const int16_t* T = ka.pair + (size_t)node * 64;
+      v = 0.0f;
+      if ((pod.flags & PF_NODE_BINPACK) && (nflags & NF_METAX_LOSS)) v = __fsub_rn(2000.0f, (float)(cnt < 32 ? (int)T[cnt] : 0));
+      else if ((pod.flags & PF_NODE_SPREAD) && (nflags & NF_METAX_SCORE)) v = __fsub_rn(2000.0f, (float)(cnt < 32 ? (int)T[32 + cnt] : 0));
+    }
     devScore = __fadd_rn(devScore, v);
   }
   *score_out = __fadd_rn(pre, devScore);

@@ -359,9 +359,47 @@ bool decode_node_json(const std::string& s, std::vector<Device>& out, std::strin
   return true;
 }
 
+// ---- json.Unmarshal into map[int]int (parseMetaxAnnos, metax/device.go:168-183) --------------------------
+// false on ANY error, as the caller there turns every error into 0: a syntax error, a document that is not an object
+// (null is fine and leaves the map empty), a key strconv.ParseInt rejects, a value that is not an integer number
+// (null is fine and stores 0).  A later duplicate key wins.
+bool decode_int_map(const std::string& s, std::vector<std::pair<int64_t, int64_t>>& out) {
+  out.clear();
+  JParser p(s);
+  JV doc;
+  if (!p.document(doc)) return false;
+  if (doc.kind == JV::Null) return true;
+  if (doc.kind != JV::Obj) return false;
+  bool ok = true;
+  for (auto& kv : doc.o) {
+    int64_t k = 0, v = 0;
+    std::string e;
+    if (!parse_int(kv.first, 64, "ParseInt", k, e)) { ok = false; continue; }
+    if (kv.second.kind == JV::Num) { if (!num_to_int(kv.second, 64, false, v)) { ok = false; continue; } }
+    else if (kv.second.kind != JV::Null) { ok = false; continue; }
+    bool found = false;
+    for (auto& o : out) if (o.first == k) { o.second = v; found = true; }
+    if (!found) out.emplace_back(k, v);
+  }
+  if (!ok) out.clear();
+  return ok;
+}
+
 // ---- vendors without a register annotation: devices derived from the node's capacity -----------------------
 bool devices_from_capacity(int kind, const std::string& node, int64_t cores, int64_t memory, std::vector<Device>& out, std::string& err) {
   out.clear();
+  if (kind == 2) {                                         // metax/device.go:67-89: `cores` carries the GPU count
+    if (cores == 0) { err = "device not found metax-tech.com/gpu"; return false; }
+    for (int64_t i = 0; i < cores; i++) {
+      Device d;
+      d.index = (uint32_t)i;
+      d.id = node + "-metax-" + std::to_string(i);
+      d.count = 1; d.devmem = 65536; d.devcore = 100; d.type = "Metax-GPU"; d.numa = 0; d.health = true;
+      out.push_back(d);
+      if (out.size() > 4096) { err = "capacity yields more than 4096 cards"; out.clear(); return false; }
+    }
+    return true;
+  }
   const bool mlu = kind == 0;
   if (cores == 0) { err = std::string("device not found ") + (mlu ? "cambricon.com/mlu.smlu.vcore" : "mthreads.com/sgpu-core"); return false; }
   const int64_t per_card = mlu ? 100 : 16;                 // cores of one card

@@ -119,7 +119,10 @@ bool generate(const hs_vendor_resources& v, const hs_container_resources* c, hs_
     case HS_REQ_WHOLE_CARD:                                   // enflame/gcu.go:91-111
       memnum = 100; mempnum = 100; corenum = 100;
       break;
-    case HS_REQ_AMD: {                                        // amd/device.go:217-266: Limits only, Requests are ignored
+    case HS_REQ_METAX:                                        // metax/device.go:134-154
+      memnum = 0; mempnum = 100; corenum = 100;
+      break;
+    case HS_REQ_AMD: {                                      // amd/device.go:217-266: Limits only, Requests are ignored
       cnt = lookup_limits(c, v.count_name);
       if (!cnt || !cnt->as_int64_ok) return false;
       if (cnt->as_int64 <= 0 || cnt->as_int64 > kMaxInt32) return false;

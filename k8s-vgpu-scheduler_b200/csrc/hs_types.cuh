@@ -37,6 +37,8 @@
 #define NF_VNPU_CORE 64u
 #define NF_BASE_NV 128u     // some device of the node has Type == "NVIDIA" exactly: the key pads like a base type (score.go:71-79,246-250)
 #define NF_BASE_MLU 256u    // … Type == "MLU"
+#define NF_METAX_LOSS 512u  // the node has metax-tech.com/gpu.topology.losses: pair[0..31] = value for that many devices
+#define NF_METAX_SCORE 1024u // … gpu.topology.scores: pair[32..63]  (metax/device.go:185-214)
 
 // vendor predicate ids (device-side switch, one code path, no dispatch layer)
 enum { HV_NVIDIA = 0, HV_DCU = 1, HV_MLU = 2, HV_ASCEND0 = 3, HV_NONE = 31 };   // 5-bit ids: up to 31 registered vendors
@@ -49,7 +51,8 @@ enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
 #define EF_ASCEND910 1u     // CommonWord has prefix "Ascend910": NetworkID topology + ScoreNode
 #define EF_ASCEND910C 2u    // k.Type == "Ascend910C": module pairing
 #define EF_MIGMODE_OK 4u    // pod's vgpu-mode annotation is absent or contains "mig" (isMIGRequest)
-#define EF_WHOLE_CARD 64u   // enflame GCU's Fit (enflame/gcu.go:144-183): health, type, "in use at all" = conflict; no uuid lists, no slot count
+#define EF_METAX 128u      // metax whole GPUs: EF_MTHREADS' gates (no uuid lists reach the device) + ScoreNode from the node's tables
+#define EF_WHOLE_CARD 64u  // enflame GCU's Fit (enflame/gcu.go:144-183): health, type, "in use at all" = conflict; no uuid lists, no slot count
 #define EF_MTHREADS 32u    // mthreads' Fit (mthreads/device.go:289-405): template gates + customFilterRule (one card per pod)
 #define EF_AMD 16u         // amd's Fit (amd/device.go:279-371): whole-card memory by default, cores as a share of the card
 #define EF_COUNT_ONLY 8u   // biren's Fit (biren/device.go:190-248): gates end after mutex; the pick has Usedmem 0, Usedcores = Coresreq
@@ -76,7 +79,8 @@ struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 
 #define PF_TOPOLOGY 4u      // PolicyContains(gpuPolicy, "topology-aware")  (NVIDIA)
 #define PF_NUMA_ASSERT 8u   // nvidia.com/numa-bind parses true (assertNuma)
 #define PF_ASCEND_HAMICORE 16u // huawei.com/vnpu-mode == "hami-core"
-#define PF_DRYRUN 32u       // decide and report the devices, leave the inventory untouched (filterSimulation, scheduler.go:1156-1199)
+#define PF_NODE_BINPACK 64u // node policy == "binpack" (metax ScoreNode reads the policy string, metax/device.go:192-211)
+#define PF_DRYRUN 32u     // decide and report the devices, leave the inventory untouched (filterSimulation, scheduler.go:1156-1199)
 
 enum { OP_FILTER = 0, OP_RELEASE = 1, OP_NOP = 2 };
 

@@ -279,6 +279,11 @@ def capacity_node_devices(vendor, node, cores, memory):
     """GetNodeDevices of the two vendors that register through node CAPACITY instead of an annotation:
     cambricon (pkg/device/cambricon/device.go:209-232) and mthreads (pkg/device/mthreads/device.go:130-153).
     cores / memory = AsInt64 of Status.Capacity[<cores resource>] / [<memory resource>] (0 when absent)."""
+    if vendor == "Metax-GPU":          # metax/device.go:67-89: `cores` is the GPU count
+        if cores == 0:
+            raise ValueError("device not found metax-tech.com/gpu")
+        return [{"Index": i, "ID": "%s-metax-%d" % (node, i), "Count": 1, "Devmem": 65536, "Devcore": 100, "Type": vendor, "Numa": 0,
+                 "Health": True, "DeviceVendor": vendor} for i in range(max(cores, 0))]
     per_card, factor, infix, res = {"MLU": (100, 256, "-cambricon-mlu-", "cambricon.com/mlu.smlu.vcore"),
                                     "Mthreads": (16, 512, "-mthreads-", "mthreads.com/sgpu-core")}[vendor]
     if cores == 0:

@@ -365,7 +365,9 @@ namespace {
 // AMD: amd/device.go:279-371 — type lists like hygon, whole-card memory by default, cores as a share of the card
 // MTHREADS: mthreads/device.go:289-405 — the template gates plus customFilterRule (all containers of a pod share one card)
 // WHOLE_CARD: enflame GCU (enflame/gcu.go:144-183) — health, type, "in use at all" = conflict; no uuid lists, no slot count
-enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY, AMD, MTHREADS, WHOLE_CARD };
+// METAX: the whole-GPU "Metax-GPU" device (metax/device.go:223-334) — the template gates with no uuid lists
+//   (checkUUID is constant true, :124-126) plus the same customFilterRule as mthreads (:156-166)
+enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY, AMD, MTHREADS, WHOLE_CARD, METAX };
 
 struct FitGates {
   Vendor vendor;
@@ -566,6 +568,7 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
         case Vendor::ASCEND:
         case Vendor::WHOLE_CARD:   // enflame/gcu.go:202-204
         case Vendor::MTHREADS:     // mthreads/device.go:191-196
+        case Vendor::METAX:        // metax/device.go:117-122
         case Vendor::PLAIN:        // iluvatar/device.go:190-195
         case Vendor::COUNT_ONLY:   // biren/device.go:130-135
           found = true;
@@ -590,7 +593,7 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
       prevnuma = dev->Numa;
       tmpDevs.clear();
     }
-    if (!CheckUUID(pod.Annotations, dev->ID, g.useUUID, g.noUseUUID)) { reason["CardUuidMismatch"]++; continue; }
+    if (g.vendor != Vendor::METAX && !CheckUUID(pod.Annotations, dev->ID, g.useUUID, g.noUseUUID)) { reason["CardUuidMismatch"]++; continue; }
 
     int32_t memreq = 0;
     if (dev->Count <= dev->Used) { reason["CardTimeSlicingExhausted"]++; continue; }
@@ -646,7 +649,7 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
     if (effectiveTotalCore != 0 && dev->Usedcores == effectiveTotalCore && k.Coresreq == 0) { reason["CardComputeUnitsExhausted"]++; continue; }
     if (g.vendor == Vendor::NVIDIA && dev->Mode == "mig")
       throw std::runtime_error("oracle: MIG devices are outside the restated scope");
-    if (g.vendor == Vendor::MTHREADS && allocated) {
+    if ((g.vendor == Vendor::MTHREADS || g.vendor == Vendor::METAX) && allocated) {
       // customFilterRule, mthreads/device.go:266-276,362-366: every device an earlier container of this pod got (looked
       // up under the DEVICE's type string) must be this very device
       bool ok = true;
@@ -732,6 +735,70 @@ class NvidiaGPUDevices : public Devices {
   }
 };
 
+// parseMetaxAnnos, metax/device.go:168-183: json.Unmarshal into map[int]int, then the entry at `index`; ANY error
+// (syntax, a key that is not an integer, a value that is not an integer number) and a missing key give 0.
+// Restated for the documents the annotation holds: one object of "int": int|null pairs (or the document null); string
+// escapes inside keys are not decoded (such a key counts as an error).
+static bool ParseInt64(const std::string& v, long long& out) {   // strconv.ParseInt(v, 10, 64)
+  size_t i = 0; bool neg = false;
+  if (!v.empty() && (v[0] == '+' || v[0] == '-')) { neg = v[0] == '-'; i = 1; }
+  if (i >= v.size()) return false;
+  unsigned long long acc = 0;
+  for (; i < v.size(); i++) {
+    if (v[i] < '0' || v[i] > '9') return false;
+    unsigned long long d = (unsigned long long)(v[i] - '0');
+    if (acc > (0x8000000000000000ULL - d) / 10) return false;
+    acc = acc * 10 + d;
+  }
+  if (!neg && acc > 0x7fffffffffffffffULL) return false;
+  out = neg ? (long long)(0 - acc) : (long long)acc;
+  return true;
+}
+
+float parseMetaxAnnos(const std::string& s, int index) {
+  size_t i = 0;
+  auto ws = [&] { while (i < s.size() && (s[i] == ' ' || s[i] == '\t' || s[i] == '\n' || s[i] == '\r')) i++; };
+  std::map<long long, long long> m;
+  ws();
+  if (s.compare(i, 4, "null") == 0) { i += 4; ws(); return 0; }
+  if (i >= s.size() || s[i] != '{') return 0;
+  i++; ws();
+  if (i < s.size() && s[i] == '}') { i++; ws(); return 0; }
+  while (true) {
+    if (i >= s.size() || s[i] != '"') return 0;
+    size_t e = s.find('"', i + 1);
+    if (e == std::string::npos) return 0;
+    std::string key = s.substr(i + 1, e - i - 1);
+    if (key.find('\\') != std::string::npos) return 0;
+    long long kv;
+    if (!ParseInt64(key, kv)) return 0;
+    i = e + 1; ws();
+    if (i >= s.size() || s[i] != ':') return 0;
+    i++; ws();
+    if (s.compare(i, 4, "null") == 0) { i += 4; m[kv]; }
+    else {
+      size_t b = i;
+      if (i < s.size() && s[i] == '-') i++;
+      if (i >= s.size() || s[i] < '0' || s[i] > '9') return 0;
+      if (s[i] == '0' && i + 1 < s.size() && s[i + 1] >= '0' && s[i + 1] <= '9') return 0;   // JSON: no leading zeros
+      while (i < s.size() && s[i] >= '0' && s[i] <= '9') i++;
+      if (i < s.size() && (s[i] == '.' || s[i] == 'e' || s[i] == 'E')) return 0;            // not an integer: UnmarshalTypeError
+      long long vv;
+      if (!ParseInt64(s.substr(b, i - b), vv)) return 0;
+      m[kv] = vv;
+    }
+    ws();
+    if (i >= s.size()) return 0;
+    if (s[i] == ',') { i++; ws(); continue; }
+    if (s[i] == '}') { i++; break; }
+    return 0;
+  }
+  ws();
+  if (i != s.size()) return 0;
+  auto it = m.find(index);
+  return it == m.end() ? 0.0f : (float)it->second;
+}
+
 // iluvatar (one instance per CommonWord, iluvatar/device.go:60-83) and biren (biren/device.go:54-66)
 class PlainDevices : public Devices {
  public:
@@ -740,14 +807,27 @@ class PlainDevices : public Devices {
   FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
                 const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
                 const QuotaManager* quota) const override {
-    static const Vendor kinds[] = {Vendor::PLAIN, Vendor::COUNT_ONLY, Vendor::AMD, Vendor::MTHREADS, Vendor::WHOLE_CARD};
-    FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 4 ? v_.FitKind : 0],
+    static const Vendor kinds[] = {Vendor::PLAIN, Vendor::COUNT_ONLY, Vendor::AMD, Vendor::MTHREADS, Vendor::WHOLE_CARD, Vendor::METAX};
+    FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 5 ? v_.FitKind : 0],
                v_.CommonWord,
                v_.UseType, v_.NoUseType, v_.UseUUID, v_.NoUseUUID};
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
+  // metax/device.go:185-214: 2000 minus the node's topology loss (binpack) / score (spread) for this many devices
+  float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo) const override {
+    if (v_.FitKind != 5) return 0;
+    int sum = 0;
+    for (auto& ctr : podDevices) sum += (int)ctr.size();
+    float res = 0;
+    if (policy == "binpack") {
+      if (nodeInfo && nodeInfo->MetaxLosses) res = (float)2000 - parseMetaxAnnos(*nodeInfo->MetaxLosses, sum);
+    } else if (policy == "spread") {
+      if (nodeInfo && nodeInfo->MetaxScores) res = (float)2000 - parseMetaxAnnos(*nodeInfo->MetaxScores, sum);
+    }
+    return res;
+  }
   void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
-    // iluvatar/device.go:143-154, biren/device.go:167-177
+    // iluvatar/device.go:143-154, biren/device.go:167-177, metax/device.go:91-103
     auto it = pd.find(v_.CommonWord);
     if (it != pd.end() && !it->second.empty()) {
       std::string s = EncodePodSingleDevice(it->second);
@@ -840,7 +920,7 @@ class AscendDevices : public Devices {
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
   // ascend/device.go:388-424
-  float ScoreNode(const PodSingleDevice& podDevices, const std::string&) const override {
+  float ScoreNode(const PodSingleDevice& podDevices, const std::string&, const NodeInfo*) const override {
     if (!HasPrefix(cfg_.CommonWord, "Ascend910")) return 0;
     float score = 0;
     for (auto& containerDevices : podDevices) {
@@ -1195,7 +1275,7 @@ NodeScoreResult Scheduler::ScoreNode(const std::string& nodeID, NodeUsage& node,
   for (auto& kv : score.Devices) {
     const Devices* dev = Vendor(kv.first);
     if (!dev) continue;
-    devScore = devScore + dev->ScoreNode(kv.second, userNodePolicy);
+    devScore = devScore + dev->ScoreNode(kv.second, userNodePolicy, node.Info);
   }
   score.Score = score.Score + devScore;
   res.fit = true;

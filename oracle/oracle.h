@@ -88,6 +88,7 @@ struct NodeInfo {                  // devices.go:170-174 (+ the node annotations
   std::map<std::string, std::vector<DeviceInfo>> Devices;  // sorted vendor key = canonical rule 5
   std::optional<std::string> DeviceCordon;                  // hami.io/device-cordon
   std::optional<std::string> HamiVnpuCore;                  // hami-vnpu-core
+  std::optional<std::string> MetaxLosses, MetaxScores;      // metax-tech.com/gpu.topology.losses / .scores (metax/device.go:38-39)
 };
 
 struct ContainerDevice {           // devices.go:205-216
@@ -175,7 +176,7 @@ class Devices {
                         const Pod& pod, const NodeInfo* nodeInfo, const std::string& gpuPolicyDefault,
                         const PodDevices* allocated = nullptr, const QuotaManager* quota = nullptr) const = 0;
   virtual ResourceNames GetResourceNames() const { return {CommonWord() + "/mem", CommonWord() + "/core", 1}; }
-  virtual float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy) const { return 0; }
+  virtual float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo = nullptr) const { return 0; }
   virtual void AddResourceUsage(DeviceUsage& n, const ContainerDevice& ctr) const;
   virtual void PatchAnnotations(const Pod& pod, std::map<std::string, std::string>& annos, const PodDevices& pd) const = 0;
 };

@@ -71,6 +71,8 @@ NodeInfo toNodeInfo(const hs_node_info* n) {
   }
   if (n->device_cordon) ni.DeviceCordon = str(n->device_cordon);
   if (n->hami_vnpu_core >= 0) ni.HamiVnpuCore = n->hami_vnpu_core == 1 ? "true" : "false";
+  if (n->metax_losses) ni.MetaxLosses = str(n->metax_losses);
+  if (n->metax_scores) ni.MetaxScores = str(n->metax_scores);
   return ni;
 }
 
@@ -494,6 +496,17 @@ int32_t oracle_quota_add_usage(oracle_handle* o, const char* ns, const char* ven
   std::map<std::string, int64_t> u{{name, delta < 0 ? -delta : delta}};
   if (delta < 0) o->s->quota.RmUsage(str(ns), u); else o->s->quota.AddUsage(str(ns), u);
   return HS_OK;
+}
+float oracle_vendor_score_node(oracle_handle* o, const char* vendor, uint32_t n_picks, const char* policy, const char* metax_losses,
+                               const char* metax_scores) {
+  const Devices* v = o->s->Vendor(str(vendor));
+  if (!v) return 0;
+  NodeInfo ni;
+  if (metax_losses) ni.MetaxLosses = str(metax_losses);
+  if (metax_scores) ni.MetaxScores = str(metax_scores);
+  PodSingleDevice psd(1);
+  for (uint32_t i = 0; i < n_picks; i++) { ContainerDevice cd; cd.Idx = (int)i; cd.UUID = "d" + std::to_string(i); cd.Type = str(vendor); psd[0].push_back(cd); }
+  return v->ScoreNode(psd, str(policy), &ni);
 }
 int32_t oracle_fit_quota_scalar(oracle_handle* o, const char* ns, const char* vendor, int64_t memreq, int32_t factor, int64_t coresreq) {
   const Devices* v = o->s->Vendor(str(vendor));

@@ -82,6 +82,9 @@ int32_t oracle_quota_del(oracle_handle* o, const char* ns, const char* vendor, i
 int32_t oracle_quota_get(oracle_handle* o, const char* ns, const char* vendor, int32_t which, int64_t* limit, int64_t* used, int32_t* limit_set);
 /* test hooks for the vectors of pkg/device/quota_test.go: poke Used, and FitQuota with an explicit memory factor */
 int32_t oracle_quota_add_usage(oracle_handle* o, const char* ns, const char* vendor, int32_t which, int64_t delta);
+/* <vendor>.ScoreNode on one container of n_picks devices (metax/device.go:185-214 reads the node's two annotations) */
+float oracle_vendor_score_node(oracle_handle* o, const char* vendor, uint32_t n_picks, const char* policy, const char* metax_losses,
+                               const char* metax_scores);
 int32_t oracle_fit_quota_scalar(oracle_handle* o, const char* ns, const char* vendor, int64_t memreq, int32_t factor, int64_t coresreq);
 /* fitQuota (nvidia/device.go:666-692): tmp / allocated as flattened entries (type_key = PodDevices key). 1 = fits. */
 int32_t oracle_fit_quota(oracle_handle* o, const char* ns, uint32_t n_init, const hs_alloc_entry* tmp, uint32_t n_tmp,

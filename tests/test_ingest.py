@@ -190,7 +190,22 @@ def test_nvidia_get_node_devices_golden(impl):
             assert m[w["device"] * len(devs) + j] == w["score"]
 
 
-_CAP_FMT = {"MLU": abi.HS_REG_CAPACITY_MLU, "Mthreads": abi.HS_REG_CAPACITY_MTHREADS}
+_CAP_FMT = {"MLU": abi.HS_REG_CAPACITY_MLU, "Mthreads": abi.HS_REG_CAPACITY_MTHREADS, "Metax-GPU": abi.HS_REG_CAPACITY_METAX}
+
+
+def test_metax_capacity_node_devices_golden():
+    """metax/device_test.go TestGetNodeDevices compares Index, ID, Devcore and Devmem (its Count literal differs from the code's)."""
+    cases = gold("metax_get_node_devices")["cases"]
+    assert len(cases) == 1
+    for c in cases:
+        count = list(c["node"]["Status"]["Capacity"].values())[0]
+        want = [{k: d[k] for k in ("Index", "ID", "Devcore", "Devmem")} for d in c["expected"]]
+        ref = O.capacity_node_devices("Metax-GPU", c["node"]["ObjectMeta"]["Name"], count, 0)
+        got, err = _capacity_product("Metax-GPU", c["node"]["ObjectMeta"]["Name"], count, 0)
+        assert err is None and got == ref
+        assert [{k: d[k] for k in ("Index", "ID", "Devcore", "Devmem")} for d in got] == want
+    got, err = _capacity_product("Metax-GPU", "n", 0, 0)
+    assert got is None and "device not found metax-tech.com/gpu" in err
 _CAP_KEYS = ("Index", "ID", "Count", "Devmem", "Devcore", "Type", "Numa", "Health", "DeviceVendor")
 
 

@@ -312,3 +312,123 @@ def test_capacity_registered_nodes_gpu_parity():
     assert parity.compare(ops, ref, got, ref_snap, snap) == []
     fit_mlu = sum(1 for (k, a), r in zip(ops, ref) if k == "filter" and a["uid"].startswith("mlu-pod") and r["status"] == abi.HS_FIT)
     assert fit_mlu > 20
+
+
+# ---- metax whole GPUs ("Metax-GPU", pkg/device/metax/device.go) -------------------------------------------
+@pytest.mark.parametrize("case", load("metax_fit"), ids=[c["name"] for c in load("metax_fit")])
+def test_metax_fit(orc, case):
+    # metax/device_test.go:485-883 (TestMetaxDevices_Fit)
+    annos = case["annos"] if isinstance(case["annos"], dict) else {}
+    fit, got, reason = run_fit(orc, "Metax-GPU", case["devices"], case["request"], annos)
+    assert fit == case["wantFit"]
+    if fit:
+        assert [g[0] for g in got] == case["wantDevIDs"] and len(got) == case["wantLen"]
+    assert reason == case["wantReason"]
+
+
+def _score_node(orc, n, policy, losses=None, scores=None):
+    import ctypes as C
+    L = oa.lib()
+    L.oracle_vendor_score_node.restype = C.c_float
+    L.oracle_vendor_score_node.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_char_p, C.c_char_p]
+    b = lambda s: None if s is None else s.encode()   # noqa: E731
+    return L.oracle_vendor_score_node(orc.h, b"Metax-GPU", n, policy.encode(), b(losses), b(scores))
+
+
+def test_metax_score_node_and_parse_annos(orc):
+    # metax/device_test.go:400-483 (Test_ScoreNode) and :101-156 (TestParseMetaxAnnos: value = table[index])
+    for c in load("metax_score_node"):
+        an = c["args"]["node"]["ObjectMeta"]["Annotations"]
+        n = sum(len(ctr) for ctr in c["args"]["podDevices"])
+        got = _score_node(orc, n, c["args"]["policy"], an.get("metax-tech.com/gpu.topology.losses"), an.get("metax-tech.com/gpu.topology.scores"))
+        assert got == c["want"], c["name"]
+    cases = load("metax_parse_annos")
+    assert len(cases) == 8
+    for c in cases:
+        assert 2000 - _score_node(orc, c["index"], "binpack", losses=c["name"]) == c["value"]
+    # every error reads as 0; the policy picks the annotation; neither policy nor annotation: 0
+    for bad in ('{"1":1.5}', '{"a":1}', '[1]', '{"1":1', '{"1":"2"}', ''):
+        assert _score_node(orc, 1, "binpack", losses=bad) == 2000.0
+    assert _score_node(orc, 1, "binpack", losses='{"1":null,"01":7}') == 1993.0
+    assert _score_node(orc, 1, "spread", losses='{"1":5}') == 0.0 and _score_node(orc, 1, "other", losses='{"1":5}', scores='{"1":5}') == 0.0
+    assert _score_node(orc, 2, "spread", scores=' {"2": 300} ') == 1700.0
+
+
+def _metax_cluster(n_nodes=48, n_pods=700, seed=41):
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    rng = random.Random(seed)
+    nodes = []
+    for i in range(n_nodes):
+        name = "mx-%03d" % i
+        if i % 4 == 3:          # NVIDIA nodes in between: a Metax pod must never land there
+            devs = [{"id": "GPU-m%03d-%d" % (i, d), "index": d, "count": 10, "devmem": 81920, "devcore": 100, "type": "NVIDIA A100-SXM4-80GB",
+                     "numa": 0, "mode": "hami-core", "health": True, "vendor": "NVIDIA"} for d in range(4)]
+            nodes.append({"name": name, "devices": devs})
+            continue
+        nd = rng.choice([2, 4, 8, 8])
+        devs = [{"id": "%s-metax-%d" % (name, d), "index": d, "count": 1, "devmem": 65536, "devcore": 100, "type": "Metax-GPU", "numa": 0,
+                 "mode": "", "health": True, "vendor": "Metax-GPU"} for d in range(nd)]
+        node = {"name": name, "devices": devs}
+        table = lambda: json.dumps({str(k): rng.choice([0, 10, 110, 270, 540, 930, 1240]) for k in range(1, nd + 1) if rng.random() < 0.85})  # noqa: E731
+        r = rng.random()
+        if r < 0.75:
+            node["metax_losses"] = table()
+        if 0.15 < r < 0.9:
+            node["metax_scores"] = table()
+        if i % 11 == 5:
+            node["metax_losses"] = '{"1": 1.5}'                # a table that does not parse: every entry reads 0
+        nodes.append(node)
+    ops, live = [], []
+    for p in range(n_pods):
+        uid = "mxp-%05d" % p
+        annos = {}
+        if rng.random() < 0.7:
+            annos["hami.io/node-scheduler-policy"] = rng.choice(["binpack", "spread", "spread", "weird"])
+        if rng.random() < 0.2:
+            annos["hami.io/gpu-scheduler-policy"] = rng.choice(["binpack", "spread", "mutex"])
+        if rng.random() < 0.12:
+            req = {"key": "NVIDIA", "type": "NVIDIA", "nums": 1, "memreq": 4096, "mempct": 101, "coresreq": 10}
+        else:
+            req = {"key": "Metax-GPU", "type": "Metax-GPU", "nums": rng.choice([1, 1, 2, 2, 4, 8]), "memreq": 0, "mempct": 100, "coresreq": 100}
+        ctrs = [[req]]
+        if rng.random() < 0.08:
+            ctrs.append([dict(req, nums=1)])                   # a second container: customFilterRule + Count 1 = never fits on metax
+        ops.append(("filter", {"uid": uid, "ns": "default", "name": uid, "annotations": annos, "containers": ctrs, "n_init": 0}))
+        live.append(uid)
+        while len(live) > 40:
+            ops.append(("delete", live.pop(rng.randrange(len(live)))))
+    return {"node_policy": "binpack", "gpu_policy": "spread"}, nodes, ops
+
+
+def test_metax_cluster_oracle_prefers_low_loss_nodes():
+    cfg, nodes, ops = _metax_cluster()
+    ref, _ = parity.run_oracle(cfg, nodes, ops, snapshot=False)
+    fits = [(a, r) for (k, a), r in zip(ops, ref) if k == "filter" and r["status"] == abi.HS_FIT and a["containers"][0][0]["type"] == "Metax-GPU"]
+    assert len(fits) > 150
+    assert any(r["score"] > 1000 for _, r in fits) and any(r["score"] < 100 for _, r in fits)   # with and without the ScoreNode term
+    by_name = {n["name"]: n for n in nodes}
+    assert all(by_name[r["node"]]["devices"][0]["vendor"] == "Metax-GPU" for _, r in fits)
+    sample = fits[0][1]
+    assert "hami.io/metax-gpu-devices-allocated" in sample["annotations"] and "hami.io/metax-gpu-devices-to-allocate" in sample["annotations"]
+
+
+@pytest.mark.gpu
+def test_metax_gpu_parity():
+    cfg, nodes, ops = _metax_cluster()
+    ref, ref_snap = parity.run_oracle(cfg, nodes, ops)
+    got, snap = parity.run_engine(cfg, nodes, ops, chunk=250)
+    assert parity.compare(ops, ref, got, ref_snap, snap) == []
+    # the same inventory registered from capacity + the two annotations decides identically
+    import k8s_vgpu_scheduler_b200.engine as eng
+    e = eng.Engine(cfg.get("node_policy"), cfg.get("gpu_policy"))
+    for n in nodes:
+        if n["devices"][0]["vendor"] != "Metax-GPU":
+            e.node_upsert(n)
+            continue
+        nd = len(n["devices"])
+        assert e.node_register(n["name"], [("Metax-GPU", abi.HS_REG_CAPACITY_METAX, n.get("metax_losses"), n.get("metax_scores"), None, nd, 0)]) == nd, e.error()
+    e.run_batch(eng.PackedOps(ops))
+    got2 = [e.batch_get(i) for i in range(len(ops))]
+    e.close()
+    assert parity.compare(ops, ref, got2) == []

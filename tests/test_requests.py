@@ -128,6 +128,8 @@ def oracle_generate(v, limits, requests):
         memnum, pctn, cores = 0, 100, 0
     elif v["kind"] == abi.HS_REQ_WHOLE_CARD:     # enflame/gcu.go:91-111
         memnum, pctn, cores = 100, 100, 100
+    elif v["kind"] == abi.HS_REQ_METAX:          # metax/device.go:134-154
+        memnum, pctn, cores = 0, 100, 100
     elif v["kind"] == abi.HS_REQ_AMD:            # amd/device.go:217-266: Limits only
         cnt, mem, core = limits.get(v["count"]), limits.get(v["mem"]), limits.get(v["cores"])
         if cnt is None or not cnt[1] or cnt[0] <= 0 or cnt[0] > MAXI32:
@@ -225,12 +227,13 @@ VASTAI = _plain("Vastai", abi.HS_REQ_COUNT, "vastaitech.com/va")
 MTHREADS = _plain("Mthreads", abi.HS_REQ_MTHREADS, "mthreads.com/vgpu", "mthreads.com/sgpu-memory", "mthreads.com/sgpu-core", 512)
 GCU = _plain("GCU", abi.HS_REQ_WHOLE_CARD, "enflame.com/gcu")
 AMD = _plain("AMD", abi.HS_REQ_AMD, "amd.com/gpu", "amd.com/gpu-mem", "amd.com/gpu-core-pct")
+METAX = _plain("Metax-GPU", abi.HS_REQ_METAX, "metax-tech.com/gpu")
 
 TABLES = [("nvidia_generate_requests", NVIDIA, 15), ("hygon_generate_requests", DCU, 5), ("hygon_generate_requests_range", DCU, 2),
           ("cambricon_generate_requests", MLU, 6), ("ascend_generate_requests", ASCEND_910A, 3),
           ("ascend_generate_requests_range", ASCEND_CORE, 7),
           ("iluvatar_generate_requests", ILUVATAR, 5), ("biren_generate_requests", BIREN, 4), ("vastai_generate_requests", VASTAI, 4),
-          ("mthreads_generate_requests", MTHREADS, 8), ("gcu_generate_requests", GCU, 3)]
+          ("mthreads_generate_requests", MTHREADS, 8), ("gcu_generate_requests", GCU, 3), ("metax_generate_requests", METAX, 2)]
 
 
 @pytest.mark.parametrize("name,vendor,count", TABLES, ids=[t[0] for t in TABLES])
@@ -291,7 +294,7 @@ def test_product_matches_restatement_on_random_containers():
     rng = random.Random(42)
     vendors = [NVIDIA, dict(NVIDIA, word="NV2", factor=4, default_mem=777, default_cores=5), DCU, dict(DCU, word="DCU2", factor=3),
                MLU, ASCEND_910A, ASCEND_CORE, dict(ASCEND_CORE, word="AscF", factor=2),
-               ILUVATAR, BIREN, MTHREADS, GCU, AMD]
+               ILUVATAR, BIREN, MTHREADS, GCU, AMD, METAX]
     names = sorted({v[k] for v in vendors for k in ("count", "mem", "pct", "cores") if v[k]})
     pool = [0, 1, 2, 8, -1, -100, 100, 101, 150, 4096, 2 ** 31 - 1, 2 ** 31, 2200000000, 2 ** 32 + 50, 8388607, 8388608,
             {"_quantity": "16Gi"}, {"_quantity": "16.0Gi"}, {"_quantity": "-1m"}, {"_quantity": "1500m"}, {"_quantity": "2000m"}]

@@ -332,6 +332,7 @@ IDENTS = {
     "Ascend910CType": "Ascend910C", "Ascend910Prefix": "Ascend910",
     "VNPUModeAnnotation": "huawei.com/vnpu-mode", "VNPUModeHamiCore": "hami-core",
     "VNPUNodeSelectorAnnotation": "hami-vnpu-core",
+    "MetaxGPUDevice": "Metax-GPU", "MetaxGPUCommonWord": "Metax-GPU",
     "MthreadsGPUDevice": "Mthreads", "MthreadsUseUUID": "mthreads.ai/use-gpuuuid", "MthreadsNoUseUUID": "mthreads.ai/nouse-gpuuuid",
     "VastaiDevice": "Vastai", "VastaiUseUUID": "vastaitech.com/use-gpuuuid", "VastaiNoUseUUID": "vastaitech.com/nouse-gpuuuid",
     "EnflameGCUDevice": "GCU",
@@ -457,6 +458,11 @@ TABLES = [
     ("mthreads_fit", "pkg/device/mthreads/device_test.go", "TestDevices_Fit", "tests"),
     ("vastai_fit", "pkg/device/vastai/device_test.go", "TestDevices_Fit", "tests"),
     ("gcu_fit", "pkg/device/enflame/gcu_test.go", "TestGCUDevices_Fit", "tests"),
+    ("metax_fit", "pkg/device/metax/device_test.go", "TestMetaxDevices_Fit", "tests"),
+    ("metax_score_node", "pkg/device/metax/device_test.go", "Test_ScoreNode", "tests"),
+    ("metax_parse_annos", "pkg/device/metax/device_test.go", "TestParseMetaxAnnos", "tests"),
+    ("metax_generate_requests", "pkg/device/metax/device_test.go", "Test_GenerateResourceRequests", "tests"),
+    ("metax_get_node_devices", "pkg/device/metax/device_test.go", "TestGetNodeDevices", "tests"),
 ]
 
 
