@@ -232,7 +232,18 @@ enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
         * (checkUUID is constant true) plus mthreads' customFilterRule; plain PatchAnnotations (:91-103); ScoreNode
         * (:185-214) adds 2000 - losses[n] under node policy "binpack" and 2000 - scores[n] under "spread", n = the
         * devices the pod received, from hs_node_info.metax_losses / metax_scores                                    */
-       HS_FIT_METAX = 5 };
+       HS_FIT_METAX = 5,
+       /* AWS Neuron (pkg/device/awsneuron/device.go:443-541).  Devcore / usedcores are core BIT MASKS.  One device:
+        * health, type, uuid, slots, mutex, then popcount(Totalcore) - popcount(Usedcores) >= Coresreq; the pick's
+        * Usedcores is the mask addCoreUsage (:367-389) hands out, tracked per pod in CustomInfo["awsusageinfo"].
+        * Several devices: graphSelect (:406-441) — a free, healthy run of list positions (any start on an "inf" ring
+        * node, aligned groups of 4 / 8 / 16 elsewhere), each position mapped to the device with that Index; the picks
+        * take the whole card (Totalmem, Totalcore); failure reads "NumaNotFit".  hs_device_info.network_id carries
+        * CustomInfo["AWSNodeType"]: 1 = the instance type contains "inf" or "Inf", 0 = any other, -1 = absent.
+        * Annotations: the allocated key only; AWS_NEURON_IDS, NEURON_RESOURCE_TYPE, NEURON_ALLOC_TIME, NEURON_ALLOCATED and
+        * aws.amazon.com/predicate-node depend on the container's resource limits (:200-243), which hs_pod does not
+        * carry — the caller's own PatchAnnotations adds them from hs_filter_result.entries.                          */
+       HS_FIT_NEURON = 6 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */
@@ -387,9 +398,14 @@ enum { HS_REG_CSV = 0,    /* device.DecodeNodeDevices  (pkg/device/devices.go:31
         * AsInt64 of Status.Capacity[<cores resource>] / [<memory resource>]) and named after the node:               */
        HS_REG_CAPACITY_MLU = 2,      /* cambricon/device.go:209-232: one card per 100 cores, <node>-cambricon-mlu-<i>   */
        HS_REG_CAPACITY_MTHREADS = 3, /* mthreads/device.go:130-153: one card per 16 cores, <node>-mthreads-<i>          */
-       HS_REG_CAPACITY_METAX = 4     /* metax/device.go:67-89: capacity_cores = the GPU count, <node>-metax-<i>, Count 1;
+       HS_REG_CAPACITY_METAX = 4,    /* metax/device.go:67-89: capacity_cores = the GPU count, <node>-metax-<i>, Count 1;
                                       * `annotation` / `pair_scores` = the node's metax-tech.com/gpu.topology.losses /
                                       * .scores values or NULL (hs_node_register hands them to hs_node_info)            */
+       HS_REG_CAPACITY_NEURON = 5    /* awsneuron/device.go:156-198: capacity_cores = the DEVICE count, capacity_memory = the
+                                      * node's total core count, capacity_aux = the vendor object's coresPerAWSNeuron so far
+                                      * (0 = unknown: total / count, which the caller then keeps), `annotation` = the node's
+                                      * node.kubernetes.io/instance-type label or NULL; <node>-AWSNeuron-<i>, Count = cores
+                                      * per device, Devcore = their bit mask, network_id as HS_FIT_NEURON documents it       */
 };
 
 typedef struct hs_vendor_registration {
@@ -400,6 +416,7 @@ typedef struct hs_vendor_registration {
   const char* node_name;    /* HS_REG_CAPACITY_*: the node's name (device IDs are built from it); hs_node_register fills it in */
   int64_t     capacity_cores;
   int64_t     capacity_memory;
+  int64_t     capacity_aux; /* HS_REG_CAPACITY_NEURON only */
 } hs_vendor_registration;
 
 /* One ContainerDevice of a decoded / collapsed PodDevices (devices.go:205-216): uuid NULL marks an EMPTY

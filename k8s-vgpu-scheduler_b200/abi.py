@@ -32,7 +32,8 @@ class hs_node_info(C.Structure):
 
 class hs_vendor_registration(C.Structure):
     _fields_ = [("vendor", C.c_char_p), ("format", C.c_int32), ("annotation", C.c_char_p), ("pair_scores", C.c_char_p),
-                ("node_name", C.c_char_p), ("capacity_cores", C.c_int64), ("capacity_memory", C.c_int64)]
+                ("node_name", C.c_char_p), ("capacity_cores", C.c_int64), ("capacity_memory", C.c_int64),
+                ("capacity_aux", C.c_int64)]
 
 
 class hs_pod_device(C.Structure):
@@ -45,7 +46,7 @@ class hs_sim_node(C.Structure):
                 ("device_cordon", C.c_char_p), ("hami_vnpu_core", C.c_int8)]
 
 
-HS_REG_CSV, HS_REG_JSON, HS_REG_CAPACITY_MLU, HS_REG_CAPACITY_MTHREADS, HS_REG_CAPACITY_METAX = 0, 1, 2, 3, 4
+HS_REG_CSV, HS_REG_JSON, HS_REG_CAPACITY_MLU, HS_REG_CAPACITY_MTHREADS, HS_REG_CAPACITY_METAX, HS_REG_CAPACITY_NEURON = 0, 1, 2, 3, 4, 5
 
 
 class hs_container_request(C.Structure):
@@ -120,7 +121,7 @@ class hs_vendor_config(C.Structure):
                 ("use_type_key", C.c_char_p), ("nouse_type_key", C.c_char_p)]
 
 
-HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD, HS_FIT_METAX = 0, 1, 2, 3, 4, 5
+HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD, HS_FIT_METAX, HS_FIT_NEURON = 0, 1, 2, 3, 4, 5, 6
 
 # The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
 # (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
@@ -142,6 +143,9 @@ DEFAULT_VENDORS = [
      "hami.io/mthreads-vgpu-devices-to-allocate", "hami.io/mthreads-vgpu-devices-allocated"),
     # metax whole GPUs (metax/device.go:35-56): no uuid lists
     ("Metax-GPU", HS_FIT_METAX, None, None, "hami.io/metax-gpu-devices-to-allocate", "hami.io/metax-gpu-devices-allocated"),
+    # awsneuron/device.go:42-58,68-79 (SupportDevices only: no to-allocate key is written)
+    ("AWSNeuron", HS_FIT_NEURON, "aws.amazon.com/use-neuron-uuid", "aws.amazon.com/nouse-neuron-uuid", None,
+     "hami.io/aws-neuron-devices-allocated"),
 ]
 
 

@@ -140,6 +140,7 @@ struct VendorInfo {
   bool count_only = false;  // biren's Fit: no memory / core gates (EF_COUNT_ONLY)
   bool whole_card = false;  // enflame GCU's Fit: a card in use at all is a conflict (EF_WHOLE_CARD)
   bool mthreads = false;    // mthreads' Fit: template gates + customFilterRule; its own annotation set (EF_MTHREADS)
+  bool neuron = false;      // AWS Neuron: core bit masks, graphSelect for several devices, per-pod awsusageinfo state (EF_NEURON)
   bool metax = false;       // metax whole GPUs: mthreads' gates without uuid lists + ScoreNode from the node's annotations (EF_METAX)
   bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
@@ -472,6 +473,7 @@ std::array<uint64_t, 4> entry_masks(hs_handle* h, const VendorInfo* v, const std
     if (h->types[t] == ktype) m[1] |= 1ull << t;                              // gpu_policy.go:203
     bool allow = true;
     if (v && !v->use_type.empty()) allow = checkType(hu ? &use : nullptr, hn ? &nouse : nullptr, h->types_upper[t]);
+    if (v && v->neuron) allow = h->types[t].find(ktype) != std::string::npos;   // strings.Contains(dev.Type, k.Type), awsneuron/device.go:497
     if (allow) m[2] |= 1ull << t;
   }
   uint64_t modes = 0xffull;
@@ -641,6 +643,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       if (v && v->amd) e.flags |= EF_AMD;
       if (v && (v->mthreads || v->metax)) e.flags |= EF_MTHREADS;   // metax/device.go:156-166 is mthreads' customFilterRule
       if (v && v->metax) e.flags |= EF_METAX;
+      if (v && v->neuron) e.flags |= EF_NEURON;
       if (v && v->whole_card) e.flags |= EF_WHOLE_CARD;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
@@ -682,7 +685,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     const DevEntry& e = c.entries[0];
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
               !(e.flags & EF_ASCEND910)) ? 1 : 0;
-    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX))) p.fast = 0;
+    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX | EF_NEURON))) p.fast = 0;
   }
   quota_rows_for(h, c.meta.ns, p);
   if (p.q_idx[0] >= 0 || p.q_idx[1] >= 0) p.fast = 0;   // the quota check lives in the general evaluator (hs_eval.cuh)
@@ -1160,6 +1163,10 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
         }
         continue;
       }
+      if (v.neuron) {     // awsneuron/device.go:200-243: the allocated key; the AWS_NEURON_* keys need the container's resource
+        annos[v.allocated] = s;   // limits (asked by device or by core) — the caller's own PatchAnnotations adds them from the entries
+        continue;
+      }
       annos[v.to_allocate] = s;
       annos[v.allocated] = s;
       if (v.ascend) {  // ascend/device.go:221-253
@@ -1539,6 +1546,7 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.mthreads = vc.fit_kind == HS_FIT_MTHREADS;
       v.whole_card = vc.fit_kind == HS_FIT_WHOLE_CARD;
       v.metax = vc.fit_kind == HS_FIT_METAX;
+      v.neuron = vc.fit_kind == HS_FIT_NEURON;
       if (v.metax) { v.use_uuid.clear(); v.nouse_uuid.clear(); }   // checkUUID is constant true (metax/device.go:124-126)
       if (vc.use_type_key) v.use_type = vc.use_type_key;
       if (vc.nouse_type_key) v.nouse_type = vc.nouse_type_key;
@@ -1610,6 +1618,9 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
     if (s.mode_id < 0) { h->err = "more distinct device modes than supported"; return HS_ERR_UNSUPPORTED; }
     auto v = h->vendor_by_word.find(s.vendor);
     s.vendor_id = v == h->vendor_by_word.end() ? HV_NONE : v->second;
+    if (s.vendor_id != HV_NONE && h->vendors[s.vendor_id].neuron && (s.devcore > 32767 || s.devcore < 0)) {
+      h->err = "AWS Neuron core mask outside the engine's int16 allocation row"; return HS_ERR_UNSUPPORTED;
+    }
     devs.push_back(s);
   }
   // canonical rule 5: vendors in sorted key order, registration order inside a vendor

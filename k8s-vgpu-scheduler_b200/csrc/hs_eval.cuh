@@ -19,6 +19,7 @@ struct NodeWork {
   float score[HS_D];                                 // DeviceListsScore.Score
   uint32_t order;                                    // nibble i = device slot at list position i
   uint32_t mth_prev;                                 // EF_MTHREADS: device slots the pod's earlier containers (of this phase) received
+  int aws[HS_D];                                     // EF_NEURON: CustomInfo["awsusageinfo"] of the working copy, -1 = key absent
   int ndev;
 };
 
@@ -140,7 +141,8 @@ __device__ __forceinline__ uint32_t uuid_mask_lookup(const uint32_t* pool, uint3
 struct FitCtx {
   int tmp_dev[HS_D];    // tmpDevs[k.Type]: device slots in pick order
   int tmp_mem[HS_D];    // their resolved memreq
-  int tmp_cores[HS_D];  // EF_AMD only: the per-device core share (every other vendor records `cores` for all picks)
+  int tmp_cores[HS_D];  // EF_AMD / EF_NEURON: the per-device Usedcores (every other vendor records `cores` for all picks)
+  int tmp_aws[HS_D];    // EF_NEURON: the pick's CustomInfo["awsusageinfo"]
   int ntmp;
   int cores;            // k.Coresreq after the 100 clamp
 };
@@ -222,7 +224,7 @@ __device__ __forceinline__ void quota_append(QuotaAcc& q, int v, const int* tmp_
 // ascend/device.go:442-617 — one backward scan with per-vendor gates.
 // td[0..cnt) = typeDevices (device slots, sorted list order).  Returns fit; the picks are in fc.
 template <int MODE>
-__device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e, const int* td, int cnt,
+__device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const int* td, int cnt,
                         uint32_t node, uint32_t nflags, const KernelArgs& ka, FitCtx& fc, EvalOut& out, const QuotaAcc* qa) {
   const int vendor = e.vendor;
   const int qv = vendor == HV_NVIDIA ? 0 : (vendor == HV_MLU ? 1 : -1);
@@ -242,6 +244,61 @@ __device__ bool dev_fit(const NodeWork& w, const DevPod& pod, const DevEntry& e,
     for (int r = 0; r < 16; r++) out.reasons[r] = 0;
     out.fkind = FK_HIST;
     out.fcards = (uint32_t)cnt;
+  }
+  if (e.flags & EF_NEURON) {
+    // AWS Neuron, awsneuron/device.go:443-541.  Totalcore / Usedcores are core bit masks; w.aws is the working copy's
+    // CustomInfo["awsusageinfo"]; DF_NET carries CustomInfo["AWSNodeType"]: 255 absent, 1 = the instance type contains
+    // "inf"/"Inf" (a ring), 0 = any other.
+    const int require = e.coresreq;
+    if (e.nums > 1) {
+      // graphSelect (:406-441) over list POSITIONS, then the device whose Index equals each chosen position (:456-472)
+      const int count = e.nums;
+      int start_found = -1;
+      const uint32_t nt = cnt > 0 ? DF_NET(w.dflags[td[0]]) : 255u;
+      const bool ring = nt == 1u;
+      if (nt != 255u && (ring || count == 4 || count == 8 || count == 16)) {
+        for (int start = 0; start + count <= cnt && start_found < 0; start += ring ? 1 : count) {
+          bool free_run = true;
+          for (int it = start; it < start + count; it++)
+            if (w.used[td[it]] > 0 || !(w.dflags[td[it]] & DF_HEALTH)) { free_run = false; break; }
+          if (free_run) start_found = start;
+        }
+      }
+      if (start_found < 0) { REASON(8 /*NumaNotFit*/); return false; }
+      for (int pos = start_found; pos < start_found + count; pos++)
+        for (int i = 0; i < cnt; i++) {
+          const int d = td[i];
+          if ((int)PK_INDEX(w.packed[d]) != pos) continue;
+          const int prev = w.aws[d] < 0 ? 0 : w.aws[d];
+          fc.tmp_dev[fc.ntmp] = d;
+          fc.tmp_mem[fc.ntmp] = w.totmem[d];
+          fc.tmp_cores[fc.ntmp] = w.totcore[d];
+          fc.tmp_aws[fc.ntmp] = (prev == 0 && require == 2) ? 3 : ((prev == 0 && require == 1) ? 1 : 3 - prev);   // addCoreUsage, :367-389
+          fc.ntmp++;
+          break;
+        }
+      return true;
+    }
+    uint32_t useMaskN = 0xffu, nouseMaskN = 0u;
+    if (e.has_use) useMaskN = uuid_mask_lookup(ka.uuid_pool, e.use_off, e.use_cnt, node);
+    if (e.nouse_cnt) nouseMaskN = uuid_mask_lookup(ka.uuid_pool, e.nouse_off, e.nouse_cnt, node);
+    for (int i = cnt - 1; i >= 0; i--) {
+      const int d = td[i];
+      if (w.aws[d] < 0) w.aws[d] = w.cores[d];        // :485-488, before every gate
+      if (!(w.dflags[d] & DF_HEALTH)) { REASON(6); continue; }
+      if (!((e.type_allow >> PK_TYPE(w.packed[d])) & 1ull)) { REASON(0); continue; }
+      if (!((useMaskN >> d) & 1u) || ((nouseMaskN >> d) & 1u)) { REASON(1); continue; }
+      if (w.count[d] <= w.used[d]) { REASON(2); continue; }
+      if (isMutex && w.used[d] > 0) { REASON(9); continue; }
+      const int have = (w.totcore[d] > 0 ? __popc((unsigned)w.totcore[d]) : 0) - (w.cores[d] > 0 ? __popc((unsigned)w.cores[d]) : 0);
+      if (have < require) { REASON(5); continue; }     // countMaskAvailable, :357-365
+      const int prev = w.aws[d];
+      const int v = (prev == 0 && require == 2) ? 3 : ((prev == 0 && require == 1) ? 1 : 3 - prev);
+      fc.tmp_dev[0] = d; fc.tmp_mem[0] = 0; fc.tmp_cores[0] = v; fc.tmp_aws[0] = v;
+      fc.ntmp = 1;
+      return true;
+    }
+    return false;
   }
   if (isAscend) {
     if (isHAMiCore && !(nflags & NF_VNPU_CORE)) {  // ascend/device.go:469-473
@@ -509,7 +566,11 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
     bool missing_net = false;
     for (int t = 0; t < fc.ntmp; t++) {
       const int d = fc.tmp_dev[t];
-      const int pick_cores = (e.flags & EF_AMD) ? fc.tmp_cores[t] : fc.cores;
+      const int pick_cores = (e.flags & (EF_AMD | EF_NEURON)) ? fc.tmp_cores[t] : fc.cores;
+      if (e.flags & EF_NEURON) {          // awsneuron/device.go:340-355
+        if (w.aws[d] < 0) w.aws[d] = 0;
+        w.aws[d] += fc.tmp_aws[t];
+      }
       w.used[d] += 1;
       w.cores[d] += pick_cores;
       w.mem[d] += fc.tmp_mem[t];
@@ -571,6 +632,7 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
         continue;
       }
       w.order = identity;      // node.DeepCopy(): registration order, fresh usage (score.go:241)
+      for (int d = 0; d < HS_D; d++) w.aws[d] = -1;
       if (!dev_fit_container<MODE>(w, pod, ent, eb, ee, node, nflags, ka, out, score_acc, &score_zero, qa)) return false;
       if (qa) for (int v = 0; v < 2; v++) if (base_key[v] && qa->len[v] == c) qa->len[v]++;   // score.go:246-250
       for (int d = 0; d < w.ndev; d++) { w.used[d] = bu[d]; w.mem[d] = bm[d]; w.cores[d] = bc[d]; }
@@ -578,6 +640,7 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   }
   w.order = identity;
   w.mth_prev = 0;
+  for (int d = 0; d < HS_D; d++) w.aws[d] = -1;   // appNodeCopy := node.DeepCopy(): no awsusageinfo key yet (scheduler.go:684 clones CustomInfo)
   if (qa) quota_reset_lists(*qa);     // score.Devices starts empty for the app containers (score.go:321-326)
   int app_index = 0;
   for (int c = pod.n_init; c < pod.n_ctr; c++) {

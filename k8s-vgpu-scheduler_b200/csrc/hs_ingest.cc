@@ -385,6 +385,30 @@ bool decode_int_map(const std::string& s, std::vector<std::pair<int64_t, int64_t
   return ok;
 }
 
+// ---- AWS Neuron GetNodeDevices, awsneuron/device.go:156-198 ---------------------------------------------------
+bool neuron_devices_from_capacity(const std::string& node, int64_t counts, int64_t cores_total, int64_t cores_per, const char* instance_type,
+                                  std::vector<Device>& out, std::string& err) {
+  out.clear();
+  if (counts == 0) { err = "device not found aws.amazon.com/neuron"; return false; }
+  uint64_t per = (uint64_t)cores_per;
+  if (per == 0) per = (uint64_t)cores_total / (uint64_t)counts;      // uint(coresTotal) / uint(counts)
+  uint64_t mask = 0;
+  const int64_t bits = (int64_t)(int)per;                              // for i < int(coresPerAWSNeuron); all ones after 64 rounds
+  for (int64_t i = 0; i < (bits > 64 ? 64 : bits); i++) mask = mask * 2 + 1;
+  const std::string type = instance_type ? instance_type : "";          // a missing label reads "" from the map
+  const bool ring = type.find("inf") != std::string::npos || type.find("Inf") != std::string::npos;
+  for (int64_t i = 0; i < counts; i++) {
+    Device d;
+    d.index = (uint32_t)i;
+    d.id = node + "-AWSNeuron-" + std::to_string(i);
+    d.count = (int32_t)per; d.devmem = 0; d.devcore = (int32_t)mask; d.type = "AWSNeuron"; d.numa = 0; d.health = true;
+    d.network_id = ring ? 1 : 0;
+    out.push_back(d);
+    if (out.size() > 4096) { err = "capacity yields more than 4096 cards"; out.clear(); return false; }
+  }
+  return true;
+}
+
 // ---- vendors without a register annotation: devices derived from the node's capacity -----------------------
 bool devices_from_capacity(int kind, const std::string& node, int64_t cores, int64_t memory, std::vector<Device>& out, std::string& err) {
   out.clear();

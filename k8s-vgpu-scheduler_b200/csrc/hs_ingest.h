@@ -29,6 +29,9 @@ bool decode_node_json(const std::string& s, std::vector<Device>& out, std::strin
 // kind 0: cambricon GetNodeDevices (cambricon/device.go:209-232), 1: mthreads (mthreads/device.go:130-153) — the devices
 // of a node derived from its capacity; false + err when the cores resource is missing or zero
 bool devices_from_capacity(int kind, const std::string& node, int64_t cores, int64_t memory, std::vector<Device>& out, std::string& err);
+// awsneuron GetNodeDevices (awsneuron/device.go:156-198); cores_per 0 = derive from this node; network_id = 1 on "inf" nodes else 0
+bool neuron_devices_from_capacity(const std::string& node, int64_t counts, int64_t cores_total, int64_t cores_per, const char* instance_type,
+                                  std::vector<Device>& out, std::string& err);
 // json.Unmarshal into map[int]int as parseMetaxAnnos uses it (metax/device.go:168-183): false on any error
 bool decode_int_map(const std::string& json, std::vector<std::pair<int64_t, int64_t>>& out);
 // scores[i*n+j] = Scores[devs[j].id] of the pair-score record whose uuid is devs[i].id (0 where absent)

@@ -51,7 +51,8 @@ enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
 #define EF_ASCEND910 1u     // CommonWord has prefix "Ascend910": NetworkID topology + ScoreNode
 #define EF_ASCEND910C 2u    // k.Type == "Ascend910C": module pairing
 #define EF_MIGMODE_OK 4u    // pod's vgpu-mode annotation is absent or contains "mig" (isMIGRequest)
-#define EF_METAX 128u      // metax whole GPUs: EF_MTHREADS' gates (no uuid lists reach the device) + ScoreNode from the node's tables
+#define EF_NEURON 256u     // AWS Neuron's Fit (awsneuron/device.go:443-541): core bit masks, graphSelect for nums > 1, awsusageinfo state
+#define EF_METAX 128u     // metax whole GPUs: EF_MTHREADS' gates (no uuid lists reach the device) + ScoreNode from the node's tables
 #define EF_WHOLE_CARD 64u  // enflame GCU's Fit (enflame/gcu.go:144-183): health, type, "in use at all" = conflict; no uuid lists, no slot count
 #define EF_MTHREADS 32u    // mthreads' Fit (mthreads/device.go:289-405): template gates + customFilterRule (one card per pod)
 #define EF_AMD 16u         // amd's Fit (amd/device.go:279-371): whole-card memory by default, cores as a share of the card

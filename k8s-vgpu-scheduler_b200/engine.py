@@ -95,15 +95,15 @@ def _kvs(d):
     return arr, len(items)
 
 
-def _registration(vendor, fmt, annotation, pair_scores=None, node_name=None, cores=0, memory=0):
+def _registration(vendor, fmt, annotation, pair_scores=None, node_name=None, cores=0, memory=0, aux=0):
     """annotation formats: (vendor, fmt, annotation[, pair_scores]); capacity formats: (vendor, fmt, None, None, node, cores, memory)."""
-    return abi.hs_vendor_registration(abi._b(vendor), fmt, abi._b(annotation), abi._b(pair_scores), abi._b(node_name), cores, memory)
+    return abi.hs_vendor_registration(abi._b(vendor), fmt, abi._b(annotation), abi._b(pair_scores), abi._b(node_name), cores, memory, aux)
 
 
-def decode_node_devices(vendor, fmt, annotation, pair_scores=None, node_name=None, cores=0, memory=0):
+def decode_node_devices(vendor, fmt, annotation, pair_scores=None, node_name=None, cores=0, memory=0, aux=0):
     """hs_decode_node_devices (host only, no GPU): (list of DeviceInfo dicts, pair-score matrix or None)."""
     L = lib()
-    reg = _registration(vendor, fmt, annotation, pair_scores, node_name, cores, memory)
+    reg = _registration(vendor, fmt, annotation, pair_scores, node_name, cores, memory, aux)
     devs, n, pair = C.POINTER(abi.hs_device_info)(), C.c_uint32(), C.POINTER(C.c_int32)()
     rc = L.hs_decode_node_devices(C.byref(reg), C.byref(devs), C.byref(n), C.byref(pair))
     if rc != 0:

@@ -275,6 +275,23 @@ def _go_div(a, b):
     return q if (a < 0) == (b < 0) else -q
 
 
+def neuron_node_devices(node, counts, cores_total, cores_per, instance_type):
+    """AWSNeuronDevices.GetNodeDevices, pkg/device/awsneuron/device.go:156-198.  cores_per = the vendor object's
+    coresPerAWSNeuron so far (0: derived from this node); instance_type = the node.kubernetes.io/instance-type label ("" when
+    absent).  NetworkID carries CustomInfo["AWSNodeType"] as graphSelect (:414) reads it: 1 = contains "inf"/"Inf", else 0."""
+    if counts == 0:
+        raise ValueError("device not found aws.amazon.com/neuron")
+    u64 = lambda v: v & ((1 << 64) - 1)   # noqa: E731
+    per = u64(cores_per) or u64(cores_total) // u64(counts)
+    bits = _i32(per) if _i32(per) > 0 else 0   # for i < int(coresPerAWSNeuron); a mask is all ones after 64 rounds anyway
+    mask = 0
+    for _ in range(min(bits, 64)):
+        mask = u64(mask * 2 + 1)
+    ring = "inf" in (instance_type or "") or "Inf" in (instance_type or "")
+    return [{"Index": i, "ID": "%s-AWSNeuron-%d" % (node, i), "Count": _i32(per), "Devmem": 0, "Devcore": _i32(mask), "Type": "AWSNeuron",
+             "Numa": 0, "Health": True, "DeviceVendor": "AWSNeuron", "NetworkID": 1 if ring else 0} for i in range(max(counts, 0))]
+
+
 def capacity_node_devices(vendor, node, cores, memory):
     """GetNodeDevices of the two vendors that register through node CAPACITY instead of an annotation:
     cambricon (pkg/device/cambricon/device.go:209-232) and mthreads (pkg/device/mthreads/device.go:130-153).

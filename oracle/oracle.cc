@@ -799,6 +799,96 @@ float parseMetaxAnnos(const std::string& s, int index) {
   return it == m.end() ? 0.0f : (float)it->second;
 }
 
+// ---- AWS Neuron (pkg/device/awsneuron/device.go) --------------------------------------------------------------
+// Totalcore / Usedcores are core BIT MASKS; CustomInfo["awsusageinfo"] (DeviceUsage.AwsUsage here) is the mask the pod's
+// earlier containers already hold on the device.  CustomInfo["AWSNodeType"] is HasNetworkID / NetworkID (see oracle.h).
+int32_t countMaskAvailable(int32_t mask) {          // awsneuron/device.go:357-365
+  int32_t ret = 0;
+  for (int32_t tmp = mask; tmp > 0; tmp /= 2) ret += tmp % 2;
+  return ret;
+}
+int addCoreUsage(int prev /* -1 = key absent */, int require) {   // :367-389
+  const int count = prev < 0 ? 0 : prev;
+  if (count == 0) {
+    if (require == 2) return 3;
+    if (require == 1) return 1;
+  }
+  return 3 - count;
+}
+std::vector<int> continuousDeviceAvailable(const std::vector<DeviceUsage*>& devices, int start, int count) {   // :390-404
+  if ((int)devices.size() < start + count) return {};
+  std::vector<int> res;
+  for (int it = start; it < start + count; it++) {
+    if (devices[it]->Used > 0 || !devices[it]->Health) return {};
+    res.push_back(it);
+  }
+  return res;
+}
+std::vector<int> graphSelect(const std::vector<DeviceUsage*>& devices, int count) {   // :406-441
+  if (devices.empty() || !devices[0]->HasNetworkID) return {};
+  if (devices[0]->NetworkID == 1) {               // instance type contains "inf" / "Inf": a ring, any start
+    for (int start = 0; start < (int)devices.size(); start++) {
+      auto res = continuousDeviceAvailable(devices, start, count);
+      if (!res.empty()) return res;
+    }
+    return {};
+  }
+  if (count == 1 || count == 4 || count == 8 || count == 16) {
+    for (int start = 0; start < (int)devices.size(); start += count) {
+      auto res = continuousDeviceAvailable(devices, start, count);
+      if (!res.empty()) return res;
+    }
+  }
+  return {};
+}
+FitResult fitNeuron(const FitGates& g, const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request,
+                    const Pod& pod, const std::string& gpuPolicyDefault) {   // :443-541
+  const ContainerDeviceRequest& k = request;
+  std::map<std::string, int> reason;
+  ContainerDevices tmpDevs;
+  const bool isMutex = PolicyContains(GetGPUSchedulerPolicyByPod(gpuPolicyDefault, pod), "mutex");
+  if (k.Nums > 1) {
+    std::vector<int> alloc = graphSelect(devices, (int)request.Nums);
+    if (alloc.empty()) {
+      reason["NumaNotFit"]++;
+      FitResult r; r.fit = false; r.reason = GenReason(reason, (int)devices.size());
+      return r;
+    }
+    for (int dev : alloc)
+      for (auto val : devices)
+        if (val->Index == (unsigned)dev) {
+          ContainerDevice cd;
+          cd.Idx = (int)val->Index; cd.UUID = val->ID; cd.Type = request.Type;
+          cd.Usedmem = val->Totalmem; cd.Usedcores = val->Totalcore;
+          cd.AwsUsage = addCoreUsage(val->AwsUsage, (int)k.Coresreq);
+          tmpDevs.push_back(cd);
+          break;
+        }
+    FitResult r; r.fit = true; r.devs = tmpDevs;
+    return r;
+  }
+  for (int i = (int)devices.size() - 1; i >= 0; i--) {
+    DeviceUsage* dev = devices[i];
+    if (dev->AwsUsage < 0) dev->AwsUsage = (int)dev->Usedcores;        // written before any gate, also on unhealthy devices
+    if (!dev->Health) { reason["CardNotHealth"]++; continue; }
+    if (!Contains(dev->Type, k.Type)) { reason["CardTypeMismatch"]++; continue; }
+    if (k.Type != g.commonWord) { reason["CardTypeMismatch"]++; continue; }   // checkType, :268-273
+    if (!CheckUUID(pod.Annotations, dev->ID, g.useUUID, g.noUseUUID)) { reason["CardUuidMismatch"]++; continue; }
+    if (dev->Count <= dev->Used) { reason["CardTimeSlicingExhausted"]++; continue; }
+    if (isMutex && dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+    if (i32sub(countMaskAvailable(dev->Totalcore), countMaskAvailable(dev->Usedcores)) < k.Coresreq) { reason["CardInsufficientCore"]++; continue; }
+    ContainerDevice cd;
+    cd.Idx = (int)dev->Index; cd.UUID = dev->ID; cd.Type = k.Type; cd.Usedmem = 0;
+    cd.AwsUsage = addCoreUsage(dev->AwsUsage, (int)k.Coresreq);
+    cd.Usedcores = (int32_t)cd.AwsUsage;
+    tmpDevs.push_back(cd);
+    FitResult r; r.fit = true; r.devs = tmpDevs;
+    return r;
+  }
+  FitResult r; r.fit = false; r.reason = GenReason(reason, (int)devices.size());
+  return r;
+}
+
 // iluvatar (one instance per CommonWord, iluvatar/device.go:60-83) and biren (biren/device.go:54-66)
 class PlainDevices : public Devices {
  public:
@@ -811,7 +901,15 @@ class PlainDevices : public Devices {
     FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 5 ? v_.FitKind : 0],
                v_.CommonWord,
                v_.UseType, v_.NoUseType, v_.UseUUID, v_.NoUseUUID};
+    if (v_.FitKind == 6) return fitNeuron(g, devices, request, pod, def);
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
+  }
+  void AddResourceUsage(DeviceUsage& n, const ContainerDevice& ctr) const override {
+    Devices::AddResourceUsage(n, ctr);
+    if (v_.FitKind == 6) {                       // awsneuron/device.go:340-355
+      if (n.AwsUsage < 0) n.AwsUsage = 0;
+      if (ctr.AwsUsage >= 0) n.AwsUsage += ctr.AwsUsage;
+    }
   }
   // metax/device.go:185-214: 2000 minus the node's topology loss (binpack) / score (spread) for this many devices
   float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo) const override {
@@ -831,6 +929,13 @@ class PlainDevices : public Devices {
     auto it = pd.find(v_.CommonWord);
     if (it != pd.end() && !it->second.empty()) {
       std::string s = EncodePodSingleDevice(it->second);
+      if (v_.FitKind == 6) {
+        // awsneuron/device.go:200-243: the allocated key only.  AWS_NEURON_IDS / NEURON_RESOURCE_TYPE / NEURON_ALLOC_TIME /
+        // NEURON_ALLOCATED / predicate-node depend on the container's resource LIMITS (asked by device or by core), which
+        // the path's input does not carry: the caller's own PatchAnnotations adds them from the returned PodDevices.
+        annos[v_.Allocated] = s;
+        return;
+      }
       if (v_.FitKind == 3) {
         // mthreads/device.go:155-177: only the allocated key; the card indices of the LAST container that got devices;
         // the node again under its own key; a timestamp (blanked, canonical rule 6)

@@ -65,8 +65,9 @@ struct DeviceUsage {               // devices.go:106-125
   int Numa = 0;
   std::string Type;
   bool Health = true;
-  bool HasNetworkID = false;       // CustomInfo["NetworkID"] present
-  int NetworkID = 0;
+  bool HasNetworkID = false;       // CustomInfo["NetworkID"] present; AWSNeuron: CustomInfo["AWSNodeType"] present …
+  int NetworkID = 0;               // … and 1 when that instance type contains "inf"/"Inf" (ring), else 0
+  int AwsUsage = -1;               // CustomInfo["awsusageinfo"] (awsneuron/device.go:340-355,485-488), -1 = key absent
 };
 
 struct DeviceInfo {                // devices.go:127-144
@@ -97,6 +98,7 @@ struct ContainerDevice {           // devices.go:205-216
   int32_t Usedmem = 0, Usedcores = 0, Slots = 0;
   bool HasNetworkID = false;       // CustomInfo carried by the Ascend Fit (ascend/device.go:573)
   int NetworkID = 0;
+  int AwsUsage = -1;               // CustomInfo["awsusageinfo"] set by the AWSNeuron Fit, -1 = absent
 };
 
 struct ContainerDeviceRequest {    // devices.go:222-228

@@ -193,6 +193,30 @@ def test_nvidia_get_node_devices_golden(impl):
 _CAP_FMT = {"MLU": abi.HS_REG_CAPACITY_MLU, "Mthreads": abi.HS_REG_CAPACITY_MTHREADS, "Metax-GPU": abi.HS_REG_CAPACITY_METAX}
 
 
+def test_neuron_capacity_node_devices_product_vs_oracle():
+    """awsneuron GetNodeDevices (awsneuron/device.go:156-198): device count, total cores, the sticky cores-per-device and the
+    instance-type label in; IDs, Count, the core bit mask and the ring flag out."""
+    rng = random.Random(5)
+    keys = ("Index", "ID", "Count", "Devmem", "Devcore", "Type", "Numa", "Health", "DeviceVendor", "NetworkID")
+    for _ in range(400):
+        counts = rng.choice([0, 1, 2, 4, 8, 16])
+        total = rng.choice([0, counts, counts * 2, counts * 2 + 1, 32, 7])
+        per = rng.choice([0, 0, 1, 2, 4, 8])
+        itype = rng.choice(["inf2.48xlarge", "trn1.32xlarge", "Inf1", "", None, "m5.large"])
+        try:
+            want = O.neuron_node_devices("n1", counts, total, per, itype)
+        except ValueError as e:
+            with pytest.raises(eng.IngestError) as ei:
+                eng.decode_node_devices("AWSNeuron", abi.HS_REG_CAPACITY_NEURON, itype, None, "n1", counts, total, per)
+            assert str(e) in str(ei.value)
+            continue
+        devs, _ = eng.decode_node_devices("AWSNeuron", abi.HS_REG_CAPACITY_NEURON, itype, None, "n1", counts, total, per)
+        assert [{k: d[k] for k in keys} for d in devs] == want, (counts, total, per, itype)
+    # awsneuron/device_test.go:244-293 (Test_GetNodeDevices): node "test", label inf2, neuron 1, neuroncore 2
+    one = O.neuron_node_devices("test", 1, 2, 0, "inf2")
+    assert (one[0]["ID"], one[0]["Count"], one[0]["Devmem"], one[0]["Devcore"], one[0]["NetworkID"]) == ("test-AWSNeuron-0", 2, 0, 3, 1)
+
+
 def test_metax_capacity_node_devices_golden():
     """metax/device_test.go TestGetNodeDevices compares Index, ID, Devcore and Devmem (its Count literal differs from the code's)."""
     cases = gold("metax_get_node_devices")["cases"]

@@ -432,3 +432,119 @@ def test_metax_gpu_parity():
     got2 = [e.batch_get(i) for i in range(len(ops))]
     e.close()
     assert parity.compare(ops, ref, got2) == []
+
+
+# ---- AWS Neuron (pkg/device/awsneuron/device.go) -----------------------------------------------------------
+def _neuron_gold():
+    return json.load(open(os.path.join(ROOT, "tests", "golden", "ingest_funcs.json")))["awsneuron"]
+
+
+@pytest.mark.parametrize("case", _neuron_gold()["fit"], ids=[c["name"] for c in _neuron_gold()["fit"]])
+def test_awsneuron_fit(orc, case):
+    # awsneuron/device_test.go:876-1110 (TestDevices_Fit)
+    fit, got, reason = run_fit(orc, "AWSNeuron", case["devices"], case["request"], case["annos"])
+    assert fit == case["wantFit"]
+    assert len(got) == case["wantLen"]
+    if fit:
+        assert [g[0] for g in got] == case["wantDevIDs"]
+    assert reason == case["wantReason"]
+
+
+@pytest.mark.parametrize("case", _neuron_gold()["graph_select"], ids=[c["name"] for c in _neuron_gold()["graph_select"]])
+def test_awsneuron_graph_select(orc, case):
+    # awsneuron/device_test.go:814-874 (Test_graphSelect): 16 devices, the node type on device 0 only; through Fit with
+    # Nums = count the picks are the devices whose Index equals the selected positions
+    devs = []
+    for i in range(16):
+        d = {"ID": "d%d" % i, "Index": i, "Used": case["used"].get(str(i), 0), "Count": 2, "Totalcore": 3, "Type": "AWSNeuron", "Health": case["health"]}
+        if i == 0:
+            d["CustomInfo"] = {"AWSNodeType": case["node_type"]}
+        devs.append(d)
+    fit, got, reason = run_fit(orc, "AWSNeuron", devs, {"Nums": case["count"], "Type": "AWSNeuron", "Coresreq": 2}, {})
+    assert fit == bool(case["want"])
+    if fit:
+        assert [g[0] for g in got] == ["d%d" % i for i in case["want"]]
+        assert all(g[3] == 3 for g in got)                      # the whole card: Usedcores = Totalcore
+    else:
+        assert reason == "1/16 NumaNotFit"
+
+
+def _neuron_cluster(n_nodes=40, n_pods=900, seed=77):
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ingest_oracle as O
+    rng = random.Random(seed)
+    nodes, caps = [], {}
+    for i in range(n_nodes):
+        name = "nr-%03d" % i
+        if i % 5 == 4:
+            devs = [{"id": "GPU-n%03d-%d" % (i, d), "index": d, "count": 10, "devmem": 81920, "devcore": 100, "type": "NVIDIA A100-SXM4-80GB",
+                     "numa": 0, "mode": "hami-core", "health": True, "vendor": "NVIDIA"} for d in range(4)]
+            nodes.append({"name": name, "devices": devs})
+            continue
+        counts = rng.choice([2, 4, 8, 8])
+        itype = rng.choice(["inf2.48xlarge", "trn1.32xlarge", "trn1.32xlarge", "Inf1.6xlarge", ""])
+        caps[name] = (counts, counts * 2, itype)
+        devs = O.neuron_node_devices(name, counts, counts * 2, 0, itype)
+        nodes.append({"name": name, "devices": [
+            {"id": d["ID"], "index": d["Index"], "count": d["Count"], "devmem": d["Devmem"], "devcore": d["Devcore"], "type": d["Type"], "numa": 0,
+             "mode": "", "health": rng.random() > 0.06, "vendor": "AWSNeuron", "network_id": d["NetworkID"]} for d in devs]})
+    ops, live = [], []
+    for p in range(n_pods):
+        uid = "nrp-%05d" % p
+        annos = {}
+        if rng.random() < 0.35:
+            annos["hami.io/gpu-scheduler-policy"] = rng.choice(["binpack", "spread", "mutex", "binpack,numa"])
+        if rng.random() < 0.4:
+            annos["hami.io/node-scheduler-policy"] = rng.choice(["binpack", "spread"])
+        def one():
+            r = rng.random()
+            if r < 0.45:       # by core: one device, 1 or 2 cores
+                return {"key": "AWSNeuron", "type": "AWSNeuron", "nums": 1, "memreq": 0, "mempct": 0, "coresreq": rng.choice([1, 1, 2])}
+            if r < 0.9:        # by device or by many cores: whole devices
+                return {"key": "AWSNeuron", "type": "AWSNeuron", "nums": rng.choice([2, 2, 3, 4, 4, 8]), "memreq": 0, "mempct": 0, "coresreq": rng.choice([2, 2, 1])}
+            return {"key": "NVIDIA", "type": "NVIDIA", "nums": 1, "memreq": 4096, "mempct": 101, "coresreq": 10}
+        ctrs = [[one()]]
+        n_init = 0
+        if rng.random() < 0.3:
+            ctrs.append([one()])
+            if rng.random() < 0.3:
+                ctrs.append([one()])
+            if rng.random() < 0.3:
+                n_init = 1
+        if rng.random() < 0.1:
+            tgt = rng.choice([n for n in nodes if n["devices"][0]["vendor"] == "AWSNeuron"])
+            annos[rng.choice(["aws.amazon.com/use-neuron-uuid", "aws.amazon.com/nouse-neuron-uuid"])] = tgt["devices"][0]["id"]
+        ops.append(("filter", {"uid": uid, "ns": "default", "name": uid, "annotations": annos, "containers": ctrs, "n_init": n_init}))
+        live.append(uid)
+        while len(live) > 45:
+            ops.append(("delete", live.pop(rng.randrange(len(live)))))
+    return {"node_policy": "binpack", "gpu_policy": "spread"}, nodes, ops, caps
+
+
+def test_awsneuron_cluster_oracle_shape():
+    cfg, nodes, ops, _ = _neuron_cluster()
+    ref, _ = parity.run_oracle(cfg, nodes, ops, snapshot=False)
+    fits = [(a, r) for (k, a), r in zip(ops, ref) if k == "filter" and r["status"] == abi.HS_FIT and a["containers"][0][0]["type"] == "AWSNeuron"]
+    multi = [r for a, r in fits if a["containers"][0][0]["nums"] > 1]
+    single = [r for a, r in fits if a["containers"][0][0]["nums"] == 1 and len(a["containers"]) == 1]
+    assert len(multi) > 40 and len(single) > 100
+    cores = {c[0][3] for r in single for c in r["devices"]["AWSNeuron"] if c}
+    assert cores <= {0, 1, 2, 3} and {1, 3} <= cores                 # core masks, not percentages
+    assert any("NumaNotFit" in v for (k, a), r in zip(ops, ref) if k == "filter" and r["status"] == abi.HS_NOFIT for v in r["failed"].values())
+    assert set(fits[0][1]["annotations"]) >= {"hami.io/aws-neuron-devices-allocated"} and "hami.io/AWSNeuron-devices-to-allocate" not in fits[0][1]["annotations"]
+
+
+@pytest.mark.gpu
+def test_awsneuron_gpu_parity():
+    cfg, nodes, ops, caps = _neuron_cluster()
+    ref, ref_snap = parity.run_oracle(cfg, nodes, ops)
+    got, snap = parity.run_engine(cfg, nodes, ops, chunk=300)
+    assert parity.compare(ops, ref, got, ref_snap, snap) == []
+    # registered from capacity + the instance-type label: the same devices (health aside), so the same first decisions
+    import k8s_vgpu_scheduler_b200.engine as eng
+    for name, (counts, total, itype) in list(caps.items())[:6]:
+        devs, _ = eng.decode_node_devices("AWSNeuron", abi.HS_REG_CAPACITY_NEURON, itype, None, name, counts, total, 0)
+        want = next(n for n in nodes if n["name"] == name)["devices"]
+        assert [(d["ID"], d["Index"], d["Count"], d["Devcore"], d["NetworkID"]) for d in devs] == \
+               [(d["id"], d["index"], d["count"], d["devcore"], d["network_id"]) for d in want]

@@ -142,6 +142,41 @@ def amd_request_cases(ref):
     return out
 
 
+def neuron_cases(ref):
+    """pkg/device/awsneuron/device_test.go: TestDevices_Fit builds its devices with makeAWSDeviceUsage(id, index, used, count,
+    totalcore, usedcores, nodeType, health) and Test_graphSelect with makeDeviceUsages(nodeType, {index: used}, health) (16
+    devices, the node type on device 0 only) — both helper calls are expanded here."""
+    rel = "pkg/device/awsneuron/device_test.go"
+    src = open(os.path.join(ref, rel)).read()
+    out = {"fit": [], "graph_select": []}
+    body = X.find_func(src, "TestDevices_Fit")
+    base = src[:src.index(body)].count("\n") + 1
+    starts = [m.start() for m in re.finditer(r'\n\t\t\{\n\t\t\tname:', body)] + [body.index("for _, test := range tests")]
+    for a, b in zip(starts, starts[1:]):
+        blk = body[a:b]
+        devs = [{"ID": m.group(1), "Index": int(m.group(2)), "Used": int(m.group(3)), "Count": int(m.group(4)), "Totalcore": int(m.group(5)),
+                 "Usedcores": int(m.group(6)), "Type": "AWSNeuron", "Health": m.group(8) == "true", "CustomInfo": {"AWSNodeType": m.group(7)}}
+                for m in re.finditer(r'makeAWSDeviceUsage\("([^"]+)", (\d+), (\d+), (\d+), (\d+), (\d+), "([^"]*)", (true|false)\)', blk)]
+        req = {k: int(v) for k, v in re.findall(r'\b(Nums|Memreq|MemPercentagereq|Coresreq):\s*(\d+)', blk)}
+        t = re.search(r'Type:\s*(AWSNeuronDevice|"[^"]*")', blk).group(1)
+        req["Type"] = "AWSNeuron" if t == "AWSNeuronDevice" else t.strip('"')
+        annos = dict(re.findall(r'"([^"]+)":\s*"([^"]*)"', re.search(r'annos:\s*map\[string\]string\{([^}]*)\}', blk).group(1)))
+        out["fit"].append({"name": re.search(r'name:\s*"([^"]+)"', blk).group(1), "source": "%s:%d" % (rel, base + body[:a].count("\n") + 1),
+                           "devices": devs, "request": req, "annos": annos,
+                           "wantFit": re.search(r'wantFit:\s*(true|false)', blk).group(1) == "true",
+                           "wantLen": int(re.search(r'wantLen:\s*(\d+)', blk).group(1)),
+                           "wantDevIDs": re.findall(r'"([^"]+)"', re.search(r'wantDevIDs:\s*\[\]string\{([^}]*)\}', blk).group(1)),
+                           "wantReason": re.search(r'wantReason:\s*"([^"]*)"', blk).group(1)})
+    body = X.find_func(src, "Test_graphSelect")
+    base = src[:src.index(body)].count("\n") + 1
+    for m in re.finditer(r'name:\s*"([^"]+)".*?makeDeviceUsages\("([^"]*)", (nil|map\[int\]int32\{[^}]*\}), (true|false)\),\s*c:\s*(\d+),.*?want1:\s*\[\]int\{([^}]*)\}', body, re.S):
+        used = {} if m.group(3) == "nil" else {int(k): int(v) for k, v in re.findall(r'(\d+):\s*(\d+)', m.group(3))}
+        out["graph_select"].append({"name": m.group(1), "source": "%s:%d" % (rel, base + body[:m.start()].count("\n")), "node_type": m.group(2),
+                                    "used": {str(k): v for k, v in used.items()}, "health": m.group(4) == "true", "count": int(m.group(5)),
+                                    "want": [int(x) for x in re.findall(r'\d+', m.group(6))]})
+    return out
+
+
 def capacity_node_cases(ref):
     """cambricon / mthreads Test_GetNodeDevices: the node's capacity in, the derived DeviceInfo list out."""
     out = []
@@ -173,7 +208,7 @@ def main():
     doc = {"note": "extracted from the reference's own tests by tools/extract_golden_ingest.py",
            "init_container": init_container_cases(ref), "nvidia_get_node_devices": pair_score_cases(ref),
            "amd_fit": amd_fit_cases(ref), "capacity_node_devices": capacity_node_cases(ref),
-           "amd_generate_requests": amd_request_cases(ref)}
+           "amd_generate_requests": amd_request_cases(ref), "awsneuron": neuron_cases(ref)}
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "ingest_funcs.json")
     with open(path, "w") as f:
         json.dump(doc, f, indent=1, sort_keys=True)
