@@ -371,7 +371,9 @@ enum { HS_REQ_NVIDIA = 0, HS_REQ_DCU = 1, HS_REQ_MLU = 2, HS_REQ_ASCEND = 3,
        HS_REQ_AMD = 6,        /* amd/device.go:217-266: Limits only; cores = percent of the card, default 100     */
        HS_REQ_MTHREADS = 7,   /* mthreads/device.go:202-264: memory_factor 512; memory and cores divided by count */
        HS_REQ_WHOLE_CARD = 8, /* enflame/gcu.go:91-111: Memreq 100, MemPercentagereq 100, Coresreq 100            */
-       HS_REQ_METAX = 9       /* metax/device.go:134-154: Memreq 0, MemPercentagereq 100, Coresreq 100            */
+       HS_REQ_METAX = 9,      /* metax/device.go:134-154: Memreq 0, MemPercentagereq 100, Coresreq 100            */
+       HS_REQ_NEURON = 10     /* awsneuron/device.go:287-334: by device (count_name) or by NeuronCore (cores_name, split
+                               * over devices); default_cores = the vendor object's coresPerAWSNeuron                */
 };
 typedef struct hs_vendor_resources {
   const char* common_word;             /* becomes the request's key and Type                                  */

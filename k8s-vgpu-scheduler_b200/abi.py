@@ -112,7 +112,7 @@ class hs_vendor_resources(C.Structure):
 
 
 HS_REQ_NVIDIA, HS_REQ_DCU, HS_REQ_MLU, HS_REQ_ASCEND = 0, 1, 2, 3
-HS_REQ_ILUVATAR, HS_REQ_COUNT, HS_REQ_AMD, HS_REQ_MTHREADS, HS_REQ_WHOLE_CARD, HS_REQ_METAX = 4, 5, 6, 7, 8, 9
+HS_REQ_ILUVATAR, HS_REQ_COUNT, HS_REQ_AMD, HS_REQ_MTHREADS, HS_REQ_WHOLE_CARD, HS_REQ_METAX, HS_REQ_NEURON = 4, 5, 6, 7, 8, 9, 10
 
 
 class hs_vendor_config(C.Structure):

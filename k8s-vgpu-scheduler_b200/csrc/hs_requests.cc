@@ -32,6 +32,30 @@ const hs_quantity* lookup_limits(const hs_container_resources* c, const char* na
 
 // returns false for the zero-value ContainerDeviceRequest{}
 bool generate(const hs_vendor_resources& v, const hs_container_resources* c, hs_container_request& r) {
+  if (v.kind == HS_REQ_NEURON) {
+    // awsneuron/device.go:287-334: by device (count_name) or, when that is absent, by NeuronCore (cores_name) through
+    // splitCoreRequest (:141-154); validateResourceRequest (:115-129): an integer in (0, max]; default_cores carries the
+    // vendor object's coresPerAWSNeuron (0 until a node registered)
+    r.key = v.common_word; r.type = v.common_word; r.memreq = 0; r.mempct = 0;
+    const hs_quantity* q = lookup(c, v.count_name);
+    if (q) {
+      if (!q->as_int64_ok || q->as_int64 <= 0 || q->as_int64 > kMaxInt32) return false;
+      r.nums = (int32_t)q->as_int64;
+      r.coresreq = v.default_cores;
+      return true;
+    }
+    q = lookup(c, v.cores_name);
+    if (!q) return false;
+    if (!q->as_int64_ok || q->as_int64 <= 0 || q->as_int64 > kMaxInt32 * 2) return false;
+    const int64_t cores = q->as_int64;
+    const int64_t per = v.default_cores <= 0 ? 2 : (v.default_cores < 2 ? v.default_cores : 2);   // coresPerDevice, :131-137
+    if (cores <= per) { r.nums = 1; r.coresreq = (int32_t)cores; return true; }
+    if (cores % per != 0) return false;
+    if (cores / per > kMaxInt32) return false;
+    r.nums = (int32_t)(cores / per);
+    r.coresreq = (int32_t)per;
+    return true;
+  }
   const hs_quantity* cnt = lookup(c, v.count_name);
   if (!cnt || !cnt->as_int64_ok) return false;
   const int64_t n = cnt->as_int64;

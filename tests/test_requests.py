@@ -67,6 +67,23 @@ def oracle_generate(v, limits, requests):
         if not name:
             return None
         return limits.get(name, requests.get(name))
+    if v["kind"] == abi.HS_REQ_NEURON:           # awsneuron/device.go:287-334 (+ :115-154)
+        def valid(q, maxv):
+            return q[1] and 0 < q[0] <= maxv
+        q = get(v["count"])
+        if q is not None:
+            return {"Nums": q[0], "Type": v["word"], "Memreq": 0, "MemPercentagereq": 0, "Coresreq": v["default_cores"]} if valid(q, MAXI32) else None
+        q = get(v["cores"])
+        if q is None or not valid(q, MAXI32 * 2):
+            return None
+        per = 2 if v["default_cores"] <= 0 else min(v["default_cores"], 2)
+        if q[0] <= per:
+            nums, cores = 1, q[0]
+        elif q[0] % per or q[0] // per > MAXI32:
+            return None
+        else:
+            nums, cores = q[0] // per, per
+        return {"Nums": nums, "Type": v["word"], "Memreq": 0, "MemPercentagereq": 0, "Coresreq": cores}
     cnt = get(v["count"])
     if cnt is None or not cnt[1]:
         return None
@@ -192,8 +209,8 @@ def product_generate(vendors, limits, requests):
         return a
     la, ra = arr(limits), arr(requests)
     ctr = abi.hs_container_resources(la, len(limits), ra, len(requests))
-    out = (abi.hs_container_request * 16)()
-    n = L.hs_generate_requests(va, len(vendors), C.byref(ctr), out, 16)
+    out = (abi.hs_container_request * 32)()
+    n = L.hs_generate_requests(va, len(vendors), C.byref(ctr), out, 32)
     assert n >= 0
     return [{"Nums": out[i].nums, "Type": out[i].type.decode(), "Memreq": out[i].memreq, "MemPercentagereq": out[i].mempct,
              "Coresreq": out[i].coresreq, "key": out[i].key.decode()} for i in range(n)]
@@ -228,12 +245,14 @@ MTHREADS = _plain("Mthreads", abi.HS_REQ_MTHREADS, "mthreads.com/vgpu", "mthread
 GCU = _plain("GCU", abi.HS_REQ_WHOLE_CARD, "enflame.com/gcu")
 AMD = _plain("AMD", abi.HS_REQ_AMD, "amd.com/gpu", "amd.com/gpu-mem", "amd.com/gpu-core-pct")
 METAX = _plain("Metax-GPU", abi.HS_REQ_METAX, "metax-tech.com/gpu")
+NEURON = dict(_plain("AWSNeuron", abi.HS_REQ_NEURON, "aws.amazon.com/neuron", None, "aws.amazon.com/neuroncore"), default_cores=2)
 
 TABLES = [("nvidia_generate_requests", NVIDIA, 15), ("hygon_generate_requests", DCU, 5), ("hygon_generate_requests_range", DCU, 2),
           ("cambricon_generate_requests", MLU, 6), ("ascend_generate_requests", ASCEND_910A, 3),
           ("ascend_generate_requests_range", ASCEND_CORE, 7),
           ("iluvatar_generate_requests", ILUVATAR, 5), ("biren_generate_requests", BIREN, 4), ("vastai_generate_requests", VASTAI, 4),
-          ("mthreads_generate_requests", MTHREADS, 8), ("gcu_generate_requests", GCU, 3), ("metax_generate_requests", METAX, 2)]
+          ("mthreads_generate_requests", MTHREADS, 8), ("gcu_generate_requests", GCU, 3), ("metax_generate_requests", METAX, 2),
+          ("awsneuron_generate_requests", NEURON, 8)]
 
 
 @pytest.mark.parametrize("name,vendor,count", TABLES, ids=[t[0] for t in TABLES])
@@ -294,7 +313,8 @@ def test_product_matches_restatement_on_random_containers():
     rng = random.Random(42)
     vendors = [NVIDIA, dict(NVIDIA, word="NV2", factor=4, default_mem=777, default_cores=5), DCU, dict(DCU, word="DCU2", factor=3),
                MLU, ASCEND_910A, ASCEND_CORE, dict(ASCEND_CORE, word="AscF", factor=2),
-               ILUVATAR, BIREN, MTHREADS, GCU, AMD, METAX]
+               ILUVATAR, BIREN, MTHREADS, GCU, AMD, METAX, NEURON, dict(NEURON, word="Neuron1", default_cores=1),
+               dict(NEURON, word="Neuron0", default_cores=0)]
     names = sorted({v[k] for v in vendors for k in ("count", "mem", "pct", "cores") if v[k]})
     pool = [0, 1, 2, 8, -1, -100, 100, 101, 150, 4096, 2 ** 31 - 1, 2 ** 31, 2200000000, 2 ** 32 + 50, 8388607, 8388608,
             {"_quantity": "16Gi"}, {"_quantity": "16.0Gi"}, {"_quantity": "-1m"}, {"_quantity": "1500m"}, {"_quantity": "2000m"}]

@@ -332,7 +332,7 @@ IDENTS = {
     "Ascend910CType": "Ascend910C", "Ascend910Prefix": "Ascend910",
     "VNPUModeAnnotation": "huawei.com/vnpu-mode", "VNPUModeHamiCore": "hami-core",
     "VNPUNodeSelectorAnnotation": "hami-vnpu-core",
-    "MetaxGPUDevice": "Metax-GPU", "MetaxGPUCommonWord": "Metax-GPU",
+    "AWSNeuronDevice": "AWSNeuron", "MetaxGPUDevice": "Metax-GPU", "MetaxGPUCommonWord": "Metax-GPU",
     "MthreadsGPUDevice": "Mthreads", "MthreadsUseUUID": "mthreads.ai/use-gpuuuid", "MthreadsNoUseUUID": "mthreads.ai/nouse-gpuuuid",
     "VastaiDevice": "Vastai", "VastaiUseUUID": "vastaitech.com/use-gpuuuid", "VastaiNoUseUUID": "vastaitech.com/nouse-gpuuuid",
     "EnflameGCUDevice": "GCU",
@@ -458,6 +458,7 @@ TABLES = [
     ("mthreads_fit", "pkg/device/mthreads/device_test.go", "TestDevices_Fit", "tests"),
     ("vastai_fit", "pkg/device/vastai/device_test.go", "TestDevices_Fit", "tests"),
     ("gcu_fit", "pkg/device/enflame/gcu_test.go", "TestGCUDevices_Fit", "tests"),
+    ("awsneuron_generate_requests", "pkg/device/awsneuron/device_test.go", "Test_GenerateResourceRequests", "tests"),
     ("metax_fit", "pkg/device/metax/device_test.go", "TestMetaxDevices_Fit", "tests"),
     ("metax_score_node", "pkg/device/metax/device_test.go", "Test_ScoreNode", "tests"),
     ("metax_parse_annos", "pkg/device/metax/device_test.go", "TestParseMetaxAnnos", "tests"),
@@ -468,6 +469,8 @@ TABLES = [
 
 SOURCE_PATCHES = {
     ("pkg/device/nvidia/device_test.go", "TestGenerateResourceRequests"): [("int64(1)<<32+50", "4294967346")],
+    ("pkg/device/awsneuron/device_test.go", "Test_GenerateResourceRequests"): [("int64(math.MaxInt32)+1", "2147483648"),
+                                                                               ("int64(math.MaxInt32)*2+2", "4294967296")],
 }
 
 
