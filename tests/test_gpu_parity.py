@@ -235,3 +235,11 @@ def test_numa_bind_verdict_without_the_sort():
     ref = _check({"node_policy": "binpack", "gpu_policy": "spread"}, nodes, ops, chunk=700)
     st = [r["status"] for (k, _), r in zip(ops, ref) if k == "filter"]
     assert st.count(abi.HS_FIT) > 800 and st.count(abi.HS_NOFIT) > 100
+
+
+def test_streaming_mode_numa_bind():
+    # the same per-NUMA verdict when the inventory is streamed (more nodes than resident groups): the winner's warp
+    # runs the full sort + scan afterwards, so verdict and picks must agree there too
+    cfg, nodes, ops = _gen().config3(n_nodes=10000, n_pods=70)     # > 9 472 resident groups; the oracle needs ~50 s for it
+    assert sum(1 for k, a in ops if k == "filter" and a["annotations"].get("nvidia.com/numa-bind") == "true") > 10
+    _check(cfg, nodes, ops)
