@@ -427,16 +427,6 @@ int flush_inventory(hs_handle* h) {
   return HS_OK;
 }
 
-const std::string* find_anno(const hs_pod* pod, const char* key) {
-  static thread_local std::string tmp;
-  for (uint32_t i = 0; i < pod->n_annotations; i++) {
-    if (pod->annotations[i].key && strcmp(pod->annotations[i].key, key) == 0) {
-      tmp = pod->annotations[i].value ? pod->annotations[i].value : "";
-      return &tmp;
-    }
-  }
-  return nullptr;
-}
 bool get_anno(const hs_pod* pod, const std::string& key, std::string& out) {
   if (key.empty()) return false;
   // Go map semantics: a later duplicate key replaces an earlier one
@@ -854,7 +844,6 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
   if (to.rel > from.rel) CUDA_OK(h, cudaMemcpyAsync(h->b_rel.d + from.rel, h->b_rel.h + from.rel, (to.rel - from.rel) * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
   CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
   int done = first;
-  uint32_t alloc_base = 0;
   while (done < n_ops) {
     KernelArgs ka;
     build_kernel_args(h, ka, n_ops, alloc_cap);
@@ -888,7 +877,6 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
       if (d.status == 1 && d.fail_slot != 0xffffffffu) h->op_fail_slot[done + i] = slot_base + d.fail_slot;
     }
     done += (int)ran;
-    alloc_base = h->b_counters.h[0];
     if (done < n_ops) {
       // resume: keep the alloc cursor, clear the fail cursor
       h->b_counters.h[1] = 0; h->b_counters.h[2] = 0; h->b_counters.h[3] = 0; h->b_counters.h[5] = 0;
@@ -896,7 +884,7 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
       CUDA_OK(h, cudaMemcpyAsync(h->b_counters.d, h->b_counters.h, 8 * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
   }
-  (void)alloc_base;   // rows sit at each op's own alloc_base (a host-made prefix sum), not behind a device cursor
+  // (allocation rows sit at each op's own alloc_base, a host-made prefix sum, not behind a device cursor)
   return HS_OK;
 }
 

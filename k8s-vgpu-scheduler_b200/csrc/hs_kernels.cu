@@ -266,7 +266,7 @@ hs_decide_kernel(const KernelArgs ka) {
   __shared__ unsigned long long s_win;
 
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
   const int glane = lane & 7;                 // device slot owned by this lane
   const int gbase = lane & 24;                // first lane of this node's quarter warp
   const uint32_t gmask = 0xffu << gbase;
