@@ -348,8 +348,12 @@ bool decode_node_json(const std::string& s, std::vector<Device>& out, std::strin
       else if (key_is(k, "custominfo")) {
         if (v.kind != JV::Obj) { bad(type_err(v, "custominfo", "map[string]interface {}")); continue; }
         // map[string]any: numbers arrive as float64; Ascend reads CustomInfo["NetworkID"] (ascend/device.go:340-352)
-        for (const auto& ci : v.o)
+        d.die_strategy = false;      // a later duplicate "custominfo" replaces the earlier map
+        for (const auto& ci : v.o) {
           if (ci.first == "NetworkID" && ci.second.kind == JV::Num) d.network_id = (int32_t)std::strtod(ci.second.s.c_str(), nullptr);
+          // vastai's isDieMode (vastai/device.go:389-403): per-die state (AIC ids) that the inventory record does not carry
+          if (ci.first == "DeviceStrategy") d.die_strategy = ci.second.kind == JV::Str && ci.second.s == "die";
+        }
       }
       // unknown keys are ignored
     }
