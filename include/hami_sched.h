@@ -207,13 +207,14 @@ typedef struct hs_ascend_config {
 /* cmd/scheduler/main.go:70-71 flags + the vendor registry of
  * pkg/scheduler/config/config.go:107-251.  NVIDIA, DCU and MLU are always
  * registered; Ascend words as listed.                                       */
-/* A vendor whose Fit is one of the two plain shapes; registered next to the built-in ones.
+/* A vendor beyond NVIDIA / DCU / MLU / Ascend, registered next to the built-in ones; fit_kind names
+ * whose Fit it runs (seven kinds below).
  *   HS_FIT_TEMPLATE    iluvatar (pkg/device/iluvatar/device.go:267-371): the gate list of hygon's Fit — health, type,
  *                      uuid, slots, mutex, memory, cores, exclusive, compute units; checkType = key equals the word
  *                      (:190-195); one registration per configured CommonWord ("BI-V100", "BI-V150", "MR-V100", …)
  *   HS_FIT_COUNT_ONLY  biren (pkg/device/biren/device.go:190-248): health, type, uuid, slots, mutex only; the pick
  *                      records Usedmem 0 and Usedcores = Coresreq as requested (no clamp)
- * PatchAnnotations of all three writes EncodePodSingleDevice under the two keys (iluvatar :143-154, biren :167-177,
+ * PatchAnnotations of iluvatar, biren and amd writes EncodePodSingleDevice under the two keys (iluvatar :143-154, biren :167-177,
  * amd :120-131).
  *   HS_FIT_AMD        amd (pkg/device/amd/device.go:279-371): health, type (use/no-use type lists, :165-186), uuid,
  *                      slots, mutex; Memreq <= 0 means the whole card's memory; Coresreq > 0 is a share of the card's
