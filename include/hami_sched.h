@@ -517,6 +517,9 @@ int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* 
 int32_t hs_debug_timing(hs_handle* h, unsigned long long out[8]);
 /* Cumulative host seconds: request compile, device run + copies, result absorb, summary. */
 int32_t hs_debug_host_seconds(hs_handle* h, double out[4]);
+/* The host parser behind hs_node_info.metax_losses / metax_scores on its own (parseMetaxAnnos, metax/device.go:168-183):
+ * the table's entry for `index` as hs_node_upsert would store it; 0 for a missing key and for any document error. */
+int64_t hs_debug_metax_table(const char* json, int64_t index);
 /* Self-check of the branch-free float32 divide against the IEEE divide on n operand pairs; mismatches. */
 long long hs_debug_divcheck(unsigned long long n, unsigned long long seed);
 

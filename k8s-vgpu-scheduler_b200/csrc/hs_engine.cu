@@ -2016,6 +2016,13 @@ int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* 
 }
 
 /* Diagnostic: cumulative host seconds spent in request compile, device run + copies, result absorb, summary. */
+int64_t hs_debug_metax_table(const char* json, int64_t index) {
+  std::vector<std::pair<int64_t, int64_t>> m;
+  if (!json || !hs_ingest::decode_int_map(json, m)) return 0;
+  for (auto& kv : m) if (kv.first == index) return kv.second;
+  return 0;
+}
+
 int32_t hs_debug_host_seconds(hs_handle* h, double out[4]) {
   if (!h) return HS_ERR_INVALID;
   for (int i = 0; i < 4; i++) out[i] = h->host_s[i];

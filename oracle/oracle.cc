@@ -775,7 +775,7 @@ float parseMetaxAnnos(const std::string& s, int index) {
     i = e + 1; ws();
     if (i >= s.size() || s[i] != ':') return 0;
     i++; ws();
-    if (s.compare(i, 4, "null") == 0) { i += 4; m[kv]; }
+    if (s.compare(i, 4, "null") == 0) { i += 4; m[kv] = 0; }   // a fresh zero element is stored (encoding/json decode.go object())
     else {
       size_t b = i;
       if (i < s.size() && s[i] == '-') i++;

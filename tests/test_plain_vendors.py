@@ -548,3 +548,39 @@ def test_awsneuron_gpu_parity():
         want = next(n for n in nodes if n["name"] == name)["devices"]
         assert [(d["ID"], d["Index"], d["Count"], d["Devcore"], d["NetworkID"]) for d in devs] == \
                [(d["id"], d["index"], d["count"], d["devcore"], d["network_id"]) for d in want]
+
+
+def test_metax_table_parser_product_vs_oracle(orc):
+    """The product's json.Unmarshal-into-map[int]int (hs_ingest.cc: decode_int_map) against the oracle's parseMetaxAnnos
+    on documents a node annotation could hold, mangled ones included: any error must read as 0 on both sides."""
+    import ctypes as C
+    import k8s_vgpu_scheduler_b200.engine as eng
+    L = eng.lib()
+    L.hs_debug_metax_table.restype = C.c_int64
+    L.hs_debug_metax_table.argtypes = [C.c_char_p, C.c_int64]
+    rng = random.Random(99)
+    docs = ['{"1":0,"2":110,"3":270,"4":540,"5":580,"6":730,"7":930,"8":1240}', 'null', '{}', ' { "1" : 5 , "2" : null } ', '{"1":1.0}', '{"1":1e2}',
+            '{"+1":3}', '{"01":4,"1":9}', '{"1":9,"01":4}', '{"-1":3,"1":-7}', '{"a":1,"1":2}', '{"1":"2"}', '[1,2]', '{"1":2,}', '{"1":2', '{"1":2}x',
+            '{"1":01}', '{"1":-0}', '{"1":9223372036854775807}', '{"1":9223372036854775808}', '{"9223372036854775808":1}', '', '   ', '{"1":true}',
+            '{"1":{"2":3}}', '{"1" 2}', '{1:2}']
+    for _ in range(300):
+        n = rng.randrange(0, 6)
+        body = ",".join('"%s":%s' % (rng.choice(["0", "1", "2", "3", "8", "31", "40"]), rng.choice(["0", "10", "110", "-5", "null", "32767", "1.5", '"x"']))
+                        for _ in range(n))
+        s = "{" + body + "}"
+        if rng.random() < 0.3 and s:
+            i = rng.randrange(len(s))
+            s = s[:i] + rng.choice(["", ",", "}", "{", " ", "x", '"']) + s[i + 1:]
+        docs.append(s)
+    checked = 0
+    for doc in docs:
+        for index in (0, 1, 2, 3, 8, 31, 40, -1):
+            want = 2000.0 - _score_node(orc, index, "binpack", losses=doc) if index >= 0 else None
+            got = L.hs_debug_metax_table(doc.encode(), index)
+            if want is not None:
+                if abs(got) <= 1 << 22:
+                    assert float(got) == want, (doc, index, got, want)
+                else:                                   # beyond float32's exact integers: both sides saw the big value
+                    assert abs(want) > 1e6, (doc, index, got, want)
+                checked += 1
+    assert checked > 2000
