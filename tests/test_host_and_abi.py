@@ -81,3 +81,23 @@ def test_c1_saturates_after_96_fits():
     nofit = [r for r in res if r["status"] == abi.HS_NOFIT]
     assert len(nofit) == 904
     assert set(nofit[0]["failed"].values()) == {"8/8 CardInsufficientCore"}
+
+
+def test_header_enumerators_match_the_python_mirror():
+    """Every `HS_NAME = value` enumerator of include/hami_sched.h that abi.py mirrors must carry the same value, and the
+    vendor-facing families (fit kinds, register formats, request kinds) must be mirrored completely."""
+    import re
+    from k8s_vgpu_scheduler_b200 import abi as A
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "include", "hami_sched.h")).read()
+    text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
+    enums = {m.group(1): int(m.group(2)) for m in re.finditer(r"\b(HS_[A-Z0-9_]+)\s*=\s*(-?\d+)", text)}
+    assert len(enums) > 30
+    mirrored = 0
+    for name, value in enums.items():
+        if hasattr(A, name):
+            assert getattr(A, name) == value, name
+            mirrored += 1
+        else:
+            assert not name.startswith(("HS_FIT_", "HS_REG_", "HS_REQ_")), "abi.py lacks " + name
+    assert mirrored > 25
