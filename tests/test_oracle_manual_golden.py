@@ -141,3 +141,64 @@ def test_annotation_text():
     o.pod_delete("p")
     assert o.snapshot("n1") == [(0, 0, 0)]
     o.close()
+
+
+def test_numa_bind_verdict_is_a_per_numa_count_when_the_sort_is_numa_major():
+    """The engine decides numa-bind requests without sorting whenever the comparator is numa-major
+    (k8s-vgpu-scheduler_b200/csrc/hs_fast.cuh: fast_fit_lite, hs_types.cuh: hs_numa_major).  The claim, checked here against the
+    oracle's real sort + Fit (policy/gpu_policy.go:77-167, nvidia/device.go:715-876) on random nodes: non-topology — some
+    NUMA id holds `nums` devices that pass every gate; topology-aware — the NUMA group at the head of the list (lowest id, or
+    highest under binpack) among the devices that reach the numa check does."""
+    import ctypes as C
+    import random
+    import oracle_abi as oa
+    from oracle_abi import abi
+    rng = random.Random(2718)
+    orc = oa.Oracle("binpack", "spread")
+    L = orc.L
+    checked = {True: 0, False: 0}
+    policies = ["binpack", "spread", "numa", "binpack,numa", "spread,numa", "numa,binpack", "topology-aware", "binpack,topology-aware",
+                "topology-aware,spread"]
+    for _ in range(1500):
+        nd = rng.randrange(1, 9)
+        devs = []
+        for d in range(nd):
+            devs.append({"ID": "G%d" % d, "Index": d, "Used": rng.choice([0, 0, 1, 3]), "Count": rng.choice([1, 3, 10]), "Usedmem": rng.choice([0, 20000, 70000]),
+                         "Totalmem": 81920, "Totalcore": 100, "Usedcores": rng.choice([0, 30, 100]), "Numa": rng.randrange(0, 4),
+                         "Type": "NVIDIA A100", "Health": rng.random() > 0.15, "Mode": "hami-core"})
+        policy = rng.choice(policies)
+        nums = rng.choice([1, 2, 2, 3, 4])
+        req = {"key": "NVIDIA", "type": "NVIDIA", "nums": nums, "memreq": rng.choice([0, 8192, 30000]), "mempct": 101, "coresreq": rng.choice([0, 30, 100])}
+        if req["memreq"] == 0:
+            req["mempct"] = rng.choice([25, 100])
+        annos = {"hami.io/gpu-scheduler-policy": policy, "nvidia.com/numa-bind": "true"}
+        rarr = (abi.hs_container_request * 1)(abi.hs_container_request(b"NVIDIA", b"NVIDIA", req["nums"], req["memreq"], req["mempct"], req["coresreq"]))
+        ctr = abi.hs_container(rarr, 1)
+        p, keep = abi.build_pod({"uid": "p", "ns": "default", "name": "p", "annotations": annos, "containers": [[req]], "n_init": 0})
+        res = abi.hs_filter_result()
+        arr = oa.devs_array([oa.dev_from_go(d) for d in devs])
+        rc = L.oracle_fit_in_devices(orc.h, arr, nd, None, -1, C.byref(ctr), C.byref(p), None, C.byref(res))
+        assert rc in (0, 1), L.oracle_last_error(orc.h)
+
+        def passes(d):
+            memreq = req["memreq"] if req["memreq"] > 0 else d["Totalmem"] * req["mempct"] // 100
+            cores = min(req["coresreq"], 100)
+            return (d["Count"] > d["Used"] and d["Totalmem"] - d["Usedmem"] >= memreq and d["Totalcore"] - d["Usedcores"] >= cores and
+                    not (d["Totalcore"] == 100 and cores == 100 and d["Used"] > 0) and
+                    not (d["Totalcore"] != 0 and d["Usedcores"] == d["Totalcore"] and cores == 0))
+        reach = [d for d in devs if d["Health"]]          # health and type come before the numa check
+        topo = "topology-aware" in [t.strip() for t in policy.split(",")]
+        if nums > nd:
+            want = False                                  # NodeInsufficientDevice
+        elif topo:
+            if not reach:
+                want = False
+            else:
+                head = max(d["Numa"] for d in reach) if policy == "binpack" else min(d["Numa"] for d in reach)
+                want = sum(1 for d in reach if d["Numa"] == head and passes(d)) >= nums
+        else:
+            want = any(sum(1 for d in reach if d["Numa"] == v and passes(d)) >= nums for v in range(4))
+        assert (rc == 1) == want, (policy, nums, req, devs)
+        checked[want] += 1
+    orc.close()
+    assert checked[True] > 200 and checked[False] > 200
