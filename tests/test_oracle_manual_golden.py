@@ -202,3 +202,46 @@ def test_numa_bind_verdict_is_a_per_numa_count_when_the_sort_is_numa_major():
         checked[want] += 1
     orc.close()
     assert checked[True] > 200 and checked[False] > 200
+
+
+def test_verdict_without_numa_bind_does_not_depend_on_the_device_order():
+    """The basis of the sweep's order-free verdict (hs_fast.cuh: fast_fit_lite): without numa-bind a node fits iff at least
+    `nums` devices pass every gate, whatever the policy sorts first — checked against the oracle's sort + Fit."""
+    import ctypes as C
+    import random
+    import oracle_abi as oa
+    from oracle_abi import abi
+    rng = random.Random(1618)
+    orc = oa.Oracle("binpack", "spread")
+    checked = {True: 0, False: 0}
+    policies = ["binpack", "spread", "mutex", "numa", "binpack,numa", "topology-aware", "mutex,topology-aware", "binpack,spread", None]
+    for _ in range(1500):
+        nd = rng.randrange(1, 9)
+        devs = [{"ID": "G%d" % d, "Index": d, "Used": rng.choice([0, 0, 1, 3]), "Count": rng.choice([1, 3, 10]), "Usedmem": rng.choice([0, 20000, 70000]),
+                 "Totalmem": 81920, "Totalcore": 100, "Usedcores": rng.choice([0, 30, 100]), "Numa": rng.randrange(0, 4), "Type": "NVIDIA A100",
+                 "Health": rng.random() > 0.15, "Mode": "hami-core"} for d in range(nd)]
+        policy = rng.choice(policies)
+        nums = rng.choice([1, 2, 2, 3, 4])
+        req = {"key": "NVIDIA", "type": "NVIDIA", "nums": nums, "memreq": rng.choice([0, 8192, 30000]), "mempct": 101, "coresreq": rng.choice([0, 30, 100])}
+        if req["memreq"] == 0:
+            req["mempct"] = rng.choice([25, 100])
+        annos = {"hami.io/gpu-scheduler-policy": policy} if policy else {}
+        if rng.random() < 0.3:
+            annos["nvidia.com/numa-bind"] = "false"
+        rarr = (abi.hs_container_request * 1)(abi.hs_container_request(b"NVIDIA", b"NVIDIA", req["nums"], req["memreq"], req["mempct"], req["coresreq"]))
+        ctr = abi.hs_container(rarr, 1)
+        p, keep = abi.build_pod({"uid": "p", "ns": "default", "name": "p", "annotations": annos, "containers": [[req]], "n_init": 0})
+        res = abi.hs_filter_result()
+        rc = orc.L.oracle_fit_in_devices(orc.h, oa.devs_array([oa.dev_from_go(d) for d in devs]), nd, None, -1, C.byref(ctr), C.byref(p), None, C.byref(res))
+        assert rc in (0, 1), orc.L.oracle_last_error(orc.h)
+        mutex = policy is not None and "mutex" in [t.strip() for t in policy.split(",")]
+        memreq = lambda d: req["memreq"] if req["memreq"] > 0 else d["Totalmem"] * req["mempct"] // 100   # noqa: E731
+        cores = min(req["coresreq"], 100)
+        ok = [d for d in devs if d["Health"] and d["Count"] > d["Used"] and not (mutex and d["Used"] > 0) and
+              d["Totalmem"] - d["Usedmem"] >= memreq(d) and d["Totalcore"] - d["Usedcores"] >= cores and
+              not (cores == 100 and d["Used"] > 0) and not (d["Usedcores"] == 100 and cores == 0)]
+        want = nums <= nd and len(ok) >= nums
+        assert (rc == 1) == want, (policy, nums, req, devs)
+        checked[want] += 1
+    orc.close()
+    assert checked[True] > 200 and checked[False] > 200
