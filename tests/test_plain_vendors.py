@@ -392,9 +392,12 @@ def _metax_cluster(n_nodes=48, n_pods=700, seed=41):
         else:
             req = {"key": "Metax-GPU", "type": "Metax-GPU", "nums": rng.choice([1, 1, 2, 2, 4, 8]), "memreq": 0, "mempct": 100, "coresreq": 100}
         ctrs = [[req]]
-        if rng.random() < 0.08:
-            ctrs.append([dict(req, nums=1)])                   # a second container: customFilterRule + Count 1 = never fits on metax
-        ops.append(("filter", {"uid": uid, "ns": "default", "name": uid, "annotations": annos, "containers": ctrs, "n_init": 0}))
+        n_init = 0
+        if rng.random() < 0.16:
+            ctrs.append([dict(req, nums=1)])                   # a second app container: customFilterRule + Count 1 = never fits on metax
+            if rng.random() < 0.5:
+                n_init = 1                                     # … but an init container runs on its own copy, and its devices count in ScoreNode's sum
+        ops.append(("filter", {"uid": uid, "ns": "default", "name": uid, "annotations": annos, "containers": ctrs, "n_init": n_init}))
         live.append(uid)
         while len(live) > 40:
             ops.append(("delete", live.pop(rng.randrange(len(live)))))
