@@ -42,7 +42,7 @@ enum {
   HS_FIT_REMOTE = 3,     /* sharded mode: a node on ANOTHER rank's shard was chosen; node_index = global position */
   HS_ERR_INVALID = -1,   /* malformed argument / unsupported shape        */
   HS_ERR_CUDA = -2,      /* CUDA runtime failure; see hs_last_error       */
-  HS_ERR_UNSUPPORTED = -3,/* feature outside the built scope (MIG, quota…) */
+  HS_ERR_UNSUPPORTED = -3,/* feature outside the built scope (dynamic MIG, …) */
   HS_ERR_WEIGHTS = -4,   /* invalid hami.io/device-scoring-weights: whole Filter errors (score.go:361-364) */
   HS_ERR_NOTFOUND = -5
 };
@@ -264,7 +264,7 @@ typedef struct hs_config {
   uint8_t                 ascend_hami_vnpu_core;  /* VNPUs.HamiVnpuCore global default */
   int32_t                 cuda_device;            /* ordinal; -1 = current device      */
   uint32_t                reserve_nodes;          /* initial HBM capacity in nodes (grows on demand) */
-  const hs_vendor_config* vendors;                /* further vendors with a plain Fit; at most 15 vendors in total */
+  const hs_vendor_config* vendors;                /* further vendors with a plain Fit; at most 31 vendors in total */
   uint32_t                n_vendors;
 } hs_config;
 
@@ -506,7 +506,10 @@ int32_t hs_filter_simulate(hs_handle* h, const hs_pod* pod, const hs_sim_node* n
  * in one static device array per GPU (about 8.5 KB, held until the process exits): at most 1024 CTAs and
  * 4,194,304 nodes, larger inputs are refused with HS_ERR_UNSUPPORTED.  The first call on a device resolves
  * the array's address — make it before any stream capture.  Calls share the array: run them one after
- * the other, never overlapping on the GPU.  `cuda_stream` NULL = the engine's own stream.              */
+ * the other, never overlapping on the GPU.  The call is synchronous (it returns once the scan has finished
+ * and the result is in the caller's buffer) and it uses the handle's request-compile state like hs_filter
+ * does, so never run it concurrently with another call on the same handle.
+ * `cuda_stream` NULL = the engine's own stream.                                                         */
 int32_t hs_sweep_static(hs_handle* h, const hs_pod* pod, void* out_device16, void* cuda_stream);
 
 /* ---- measurement / diagnostic hooks (no counterpart in the reference) ----------------------- */

@@ -19,6 +19,7 @@
 #include <set>
 #include <string>
 #include <unordered_map>
+#include <unordered_set>
 #include <vector>
 
 #include "../../include/hami_sched.h"
@@ -142,6 +143,7 @@ struct VendorInfo {
   bool mthreads = false;    // mthreads' Fit: template gates + customFilterRule; its own annotation set (EF_MTHREADS)
   bool neuron = false;      // AWS Neuron: core bit masks, graphSelect for several devices, per-pod awsusageinfo state (EF_NEURON)
   bool metax = false;       // metax whole GPUs: mthreads' gates without uuid lists + ScoreNode from the node's annotations (EF_METAX)
+  int fit_kind = 0;         // HS_FIT_* as registered (hs_filter_simulate hands it on to the child handle)
   bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
 };
@@ -151,6 +153,7 @@ struct PodRec {           // podManager entry: what to subtract when the pod goe
   int4 delta[HS_D];
   bool init_released = false;   // PodInfo.InitContainerResourceReleased (pods.go:40-53)
   std::string ns;               // pod.Namespace, for quotaManager.RmUsage
+  std::vector<std::pair<std::string, int4>> parked;   // usage on devices that left the node's register annotation, by UUID
 };
 
 struct EntryMeta {
@@ -280,6 +283,8 @@ struct hs_handle {
   DBuf<long long> b_quota;
   hs_handle* sim = nullptr;             // child handle holding the transient inventory of hs_filter_simulate
   bool dry_run = false;                 // set around hs_filter_dry: ops neither release nor commit
+  size_t n_parked = 0;                  // PodRec::parked entries alive in h->pods
+  bool poisoned = false;                // a CUDA call failed while a batch was on the device: HBM and the host mirror may differ
   bool hostprof = false;                // HS_HOSTPROF=1: split the summary time by result kind, printed at hs_destroy
   double prof_s[4] = {0, 0, 0, 0};      // fit / no-fit / other / count
   double host_s[4] = {0, 0, 0, 0};      // diagnostic: cumulative host seconds in compile / device+copies / absorb / summary
@@ -1234,7 +1239,11 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
 }
 
 // Stage a RELEASE device op for `uid` (pods map or an earlier FILTER of this batch).
+// podManager (h->pods) is NOT touched here: the pod's record goes away in absorb_results, after the device has run the
+// op, so every error return in between leaves the handle as it was.  `released` remembers, for the rest of this
+// compile, which known pods already have a release staged.
 bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std::string, int>& in_batch,
+                   std::unordered_set<std::string>& released,
                    std::vector<DevPod>& pods, std::vector<int4>& rel, std::vector<OpMeta>& metas, int user_op) {
   DevPod p;
   memset(&p, 0, sizeof p);
@@ -1249,6 +1258,7 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
     in_batch.erase(ib);
   } else {
     auto it = h->pods.find(uid);
+    if (it != h->pods.end() && released.count(uid)) it = h->pods.end();
     if (it == h->pods.end()) {
       if (h->shard_world <= 1 || user_op < 0) return false;
       p.op = OP_NOP;                       // sharded: another rank may hold it; keep the op index aligned across ranks
@@ -1275,7 +1285,7 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
       memcpy(&p.e0, rd, sizeof rd);
     }
     rel_ns = it->second.ns;
-    h->pods.erase(it);
+    released.insert(uid);
   }
   quota_rows_for(h, rel_ns, p);
   OpMeta m;
@@ -1306,11 +1316,14 @@ void absorb_results(hs_handle* h, int n_ops) {
       if (p.rel_node >= 0) {
         apply_host_delta(h, p.rel_node, h->b_rel.h + p.rel_off, -1);
         quota_track(h, m.ns, p.rel_node, h->b_rel.h + p.rel_off, -1);
+        auto known = h->pods.find(m.uid);  // podManager.DelPod: only now, with the device's release done
+        if (known != h->pods.end()) { h->n_parked -= known->second.parked.size(); h->pods.erase(known); }
       } else {
         auto it = h->pods.find(m.uid);
         if (it != h->pods.end()) {
           apply_host_delta(h, it->second.node, it->second.delta, -1);
           quota_track(h, it->second.ns, it->second.node, it->second.delta, -1);
+          h->n_parked -= it->second.parked.size();
           h->pods.erase(it);
         }
       }
@@ -1322,13 +1335,25 @@ void absorb_results(hs_handle* h, int n_ops) {
 // scheduler.go:1092-1094), run them, absorb the results.
 static inline double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
+// A CUDA failure while ops are on the device leaves commits in HBM that the host mirror never absorbed (and, in the
+// pipelined mode, whole chunks of them): the handle refuses further work instead of scheduling on a wrong cache.
+int poison(hs_handle* h, int rc) {
+  if (rc == HS_ERR_CUDA && !h->poisoned) {
+    h->poisoned = true;
+    h->err += " [the batch failed on the device; this handle's usage cache can no longer be trusted: destroy it and rebuild from the informers]";
+  }
+  return rc;
+}
+
 int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
+  if (h->poisoned) { h->err = "handle is unusable after an earlier device failure (hs_destroy and rebuild it)"; return HS_ERR_CUDA; }
   const double t0 = now_s();
   std::vector<DevPod> pods;
   std::vector<DevEntry> entries;
   std::vector<uint32_t> uuid_pool;
   std::vector<int4> rel;
   std::unordered_map<std::string, int> in_batch;
+  std::unordered_set<std::string> released;   // known pods with a release staged in this batch (h->pods is untouched until absorb)
   h->metas.clear();
   h->user_first_op.assign(n_ops, -1);
   h->user_status.assign(n_ops, HS_OK);
@@ -1341,14 +1366,14 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
       if (!pod || !pod->uid) { h->user_status[i] = HS_ERR_INVALID; continue; }
       std::string uid = pod->uid;
       if (ops[i].kind == HS_OP_DELETE) {
-        if (stage_release(h, uid, in_batch, pods, rel, h->metas, (int)i)) h->user_first_op[i] = (int)pods.size() - 1;
+        if (stage_release(h, uid, in_batch, released, pods, rel, h->metas, (int)i)) h->user_first_op[i] = (int)pods.size() - 1;
         else h->user_status[i] = HS_ERR_NOTFOUND;
         continue;
       }
       int rc = compile_pod(h, pod, uuid_pool, c);
       if (rc != HS_OK) { h->user_status[i] = rc; continue; }
       if (h->dry_run) { c.pod.flags |= PF_DRYRUN; c.meta.dry = true; }   // simulation runs before TakeAndDeletePod (scheduler.go:1088-1094)
-      else stage_release(h, uid, in_batch, pods, rel, h->metas, -1);  // TakeAndDeletePod
+      else stage_release(h, uid, in_batch, released, pods, rel, h->metas, -1);  // TakeAndDeletePod
       c.pod.entry_off = (uint32_t)entries.size();
       entries.insert(entries.end(), c.entries.begin(), c.entries.end());
       c.meta.user_op = (int)i;
@@ -1414,7 +1439,7 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
       if (rc == HS_OK) rc = device_range(h, 0, n, StageMark(), staged, alloc_cap);
       if (rc == HS_OK) rc = device_end(h, n, alloc_cap);
     }
-    if (rc != HS_OK) return rc;
+    if (rc != HS_OK) return poison(h, rc);
     const double t2 = now_s();
     absorb_results(h, n);
     const double t3 = now_s();
@@ -1439,14 +1464,14 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
   compile_range(0, kChunk);
   compile_s += now_s() - tc0;
   int rc = device_begin(h, max_ops, alloc_bound);
-  if (rc != HS_OK) return rc;
+  if (rc != HS_OK) return poison(h, rc);
   StageMark uploaded;
   int first = 0;
   uint32_t next_user = kChunk;
   while (true) {
     const double td0 = now_s();
     rc = stage(uploaded);
-    if (rc != HS_OK) return rc;
+    if (rc != HS_OK) return first > 0 ? poison(h, rc) : rc;   // earlier chunks already ran on the device
     const int last = (int)pods.size();
     const StageMark from = uploaded, to = staged;
     const uint32_t cap_now = alloc_bound;
@@ -1460,7 +1485,7 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
       next_user = i1;
       compile_s += now_s() - tcc;
     }
-    if (fut.valid()) { rc = fut.get(); if (rc != HS_OK) return rc; }
+    if (fut.valid()) { rc = fut.get(); if (rc != HS_OK) return poison(h, rc); }
     device_s += now_s() - td0;
     uploaded = to;
     first = last;
@@ -1470,7 +1495,7 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
   if (n == 0) return HS_OK;
   const double te0 = now_s();
   rc = device_end(h, n, alloc_cap);
-  if (rc != HS_OK) return rc;
+  if (rc != HS_OK) return poison(h, rc);
   device_s += now_s() - te0;
   const double t2 = now_s();
   absorb_results(h, n);
@@ -1529,6 +1554,7 @@ hs_handle* hs_create(const hs_config* cfg) {
       VendorInfo& v = h->vendors.back();
       v.ascend910 = false;
       v.gate = HV_DCU;                      // iluvatar's Fit is hygon's gate list (iluvatar/device.go:267-371)
+      v.fit_kind = vc.fit_kind;
       v.count_only = vc.fit_kind == HS_FIT_COUNT_ONLY;
       v.amd = vc.fit_kind == HS_FIT_AMD;
       v.mthreads = vc.fit_kind == HS_FIT_MTHREADS;
@@ -1641,8 +1667,11 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
     vec.erase(std::remove(vec.begin(), vec.end(), ((uint32_t)slot << 8) | (uint32_t)d), vec.end());
     if (vec.empty()) h->uuid_index.erase(ns.devs[d].uuid);
   }
-  {   // the pods of this node remember their devices by slot: follow the devices to their new slots (a vanished UUID
-      // takes its share of the usage with it, exactly like the join by UUID in the reference)
+  int4 revived[HS_D];       // usage that returns with a UUID that had left this node's annotation for a while
+  for (int k = 0; k < HS_D; k++) revived[k] = make_int4(0, 0, 0, 0);
+  {   // the pods of this node remember their devices by slot: follow the devices to their new slots.  A vanished UUID
+      // takes its share of the usage with it — and brings it back when it is registered again: the reference joins
+      // pods and node devices by UUID on every rebuild (scheduler.go:773-785), so the share is parked beside the pod.
     int new_of[HS_D];
     bool identity = true;
     for (size_t d = 0; d < ns.devs.size() && d < (size_t)HS_D; d++) {
@@ -1650,13 +1679,35 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
       for (size_t k = 0; k < sorted.size(); k++) if (sorted[k].uuid == ns.devs[d].uuid) { new_of[d] = (int)k; break; }
       if (new_of[d] != (int)d) identity = false;
     }
-    if (!identity)
+    bool fresh[HS_D];
+    bool any_fresh = false;
+    for (size_t k = 0; k < sorted.size() && k < (size_t)HS_D; k++) {
+      fresh[k] = true;
+      for (size_t d = 0; d < ns.devs.size(); d++) if (ns.devs[d].uuid == sorted[k].uuid) fresh[k] = false;
+      any_fresh = any_fresh || fresh[k];
+    }
+    if (!identity || (any_fresh && h->n_parked > 0))
       for (auto& kv : h->pods) {
         if (kv.second.node != slot) continue;
         int4 moved[HS_D];
         for (int k = 0; k < HS_D; k++) moved[k] = make_int4(0, 0, 0, 0);
-        for (size_t d = 0; d < ns.devs.size() && d < (size_t)HS_D; d++)
-          if (new_of[d] >= 0) moved[new_of[d]] = kv.second.delta[d];
+        for (size_t d = 0; d < ns.devs.size() && d < (size_t)HS_D; d++) {
+          const int4& v = kv.second.delta[d];
+          if (new_of[d] >= 0) moved[new_of[d]] = v;
+          else if (v.x | v.y | v.z) { kv.second.parked.emplace_back(ns.devs[d].uuid, v); h->n_parked++; }
+        }
+        if (any_fresh && !kv.second.parked.empty())
+          for (size_t k = 0; k < sorted.size() && k < (size_t)HS_D; k++) {
+            if (!fresh[k]) continue;
+            auto& pk = kv.second.parked;
+            for (size_t i = 0; i < pk.size();) {
+              if (pk[i].first != sorted[k].uuid) { i++; continue; }
+              moved[k].x += pk[i].second.x; moved[k].y += pk[i].second.y; moved[k].z += pk[i].second.z;
+              revived[k].x += pk[i].second.x; revived[k].y += pk[i].second.y; revived[k].z += pk[i].second.z;
+              pk.erase(pk.begin() + (long)i);
+              h->n_parked--;
+            }
+          }
         for (int k = 0; k < HS_D; k++) kv.second.delta[k] = moved[k];
       }
   }
@@ -1682,6 +1733,7 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
       const DevSlot& s = ns.devs[d];
       auto ou = old_usage.find(s.uuid);
       if (ou != old_usage.end()) { dy.x = ou->second.x; dy.y = ou->second.y; dy.z = ou->second.z; }
+      else { dy.x = revived[d].x; dy.y = revived[d].y; dy.z = revived[d].z; }
       uint32_t df = DF_PRESENT | (s.health ? DF_HEALTH : 0u) | (cordoned.count(s.uuid) ? DF_CORDON : 0u) |
                     ((uint32_t)s.mode_id << 3) | ((uint32_t)(s.network_id >= 0 ? s.network_id : 255) << 8);
       dy.w = (int)df;
@@ -1794,6 +1846,7 @@ int32_t hs_pod_delete(hs_handle* h, const char* pod_uid) {
   apply_host_delta(h, it->second.node, it->second.delta, -1);
   quota_track(h, it->second.ns, it->second.node, it->second.delta, -1);
   mark_dirty(h, it->second.node);
+  h->n_parked -= it->second.parked.size();
   h->pods.erase(it);
   return HS_OK;
 }
@@ -2145,6 +2198,9 @@ uint64_t hs_launch_count(const hs_handle* h) { return h ? h->launches : 0; }
 //    rewrites the request record and zeroes the ticket itself, and the partial keys are fully
 //    overwritten before they are read.  Two calls that overlap on the GPU (different streams, or two
 //    handles on one device) would race on the array — issue them one after the other.
+//  * The call is synchronous: it waits for the scan before it returns (the request record is copied from a
+//    host stack buffer), and it rewrites the handle's request-compile state the way hs_filter does — so it
+//    is not re-entrant with any other call on the same handle.
 #define HS_STATIC_MAX_CTAS 1024
 #define HS_STATIC_MAX_NODES (1 << 22)
 #define HS_STATIC_SCRATCH_BYTES (512 + 8 * HS_STATIC_MAX_CTAS)

@@ -139,11 +139,9 @@ __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
 
 // Arg-best + grid barrier in one 16-byte L2 slot per op: {best key, arrivals}.  Warp 0 of every CTA
 // max-reduces the CTA's warp keys with shuffles; its lane 0 folds the result in with atomicMax, then
-// release-adds the CTA's arrival and polls the slot with ONE 128-bit relaxed load per round, so the
-// value that ends the spin already carries the winner (no second round trip, no L1 invalidation in
-// the spin, one poller and one polled sector per CTA).  Every CTA's max is ordered before its arrival
-// by the release, and both words share an L2 sector, so arrivals == gridDim.x implies the key is
-// final.  The launch is cooperative, so every CTA is resident.  Returns the winning key to the CTA.
+// release-adds the CTA's arrival and polls the arrival count with acquire loads (slot_poll): every
+// CTA's max is ordered before its arrival by the release, the acquire that reads the full count orders
+// the read of the key after all of them.  The launch is cooperative, so every CTA is resident.  Returns the winning key to the CTA.
 // (An all-to-all ring of per-CTA slots polled by a whole warp was measured slower: 157 pollers x 5
 // lines per round hot-spot the L2 slices and delay the arrivals themselves.)
 // Multi-GPU extension (one process per GPU, nodes sharded in contiguous blocks): the CTAs of a GPU first
@@ -153,6 +151,20 @@ __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
 // mailbox row (lane p watches rank p's word) until every word carries the epoch and takes the max — there is no
 // second publish hop.  The key embeds the GLOBAL position, so max == the canonical arg-best across ranks.  Rows of the
 // mailbox ring are reused 4 barriers later; epochs continue across launches, so nothing is ever reset.
+// Wait until every CTA of the grid has arrived at `slot`, then return the final key.  The arrivals are release-adds
+// that follow each CTA's atomicMax; the poll is an ACQUIRE load of the counter, so once it reads gridDim.x every
+// CTA's max is ordered before the load of `best` that follows (PTX memory model: release/acquire on `arrived`) —
+// the guarantee does not lean on how a 128-bit load happens to be served by an L2 sector.
+__device__ __forceinline__ unsigned long long slot_poll(OpSync* slot) {
+  uint32_t cnt;
+  do {
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(cnt) : "l"(&slot->arrived) : "memory");
+  } while (cnt < gridDim.x);
+  unsigned long long best;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(best) : "l"(&slot->best) : "memory");
+  return best;
+}
+
 #define XGPU_SPIN_LIMIT (1u << 24)       // ~10-20 s of polling before a CTA gives up on a peer (counters[6] = 1)
 __device__ __forceinline__ unsigned long long slot_argbest(const KernelArgs& ka, OpSync* slot, uint32_t b,
                                                            unsigned long long warp_key,
@@ -167,11 +179,7 @@ __device__ __forceinline__ unsigned long long slot_argbest(const KernelArgs& ka,
       if (lane == 0) {
         if (v) atomicMax(&slot->best, v);
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
-        unsigned long long best = 0, cnt;
-        do {
-          asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
-        } while ((uint32_t)cnt < gridDim.x);
-        *s_win = best;
+        *s_win = slot_poll(slot);
       }
     } else {
       const unsigned long long epoch = (unsigned long long)((ka.epoch_base + b + 1u) & 255u);
@@ -180,10 +188,7 @@ __device__ __forceinline__ unsigned long long slot_argbest(const KernelArgs& ka,
         if (v) atomicMax(&slot->best, v);
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
         if (blockIdx.x == 0) {      // the rank's leader: wait for this GPU's CTAs, then post the shard's key to every rank
-          unsigned long long best = 0, cnt;
-          do {
-            asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
-          } while ((uint32_t)cnt < gridDim.x);
+          const unsigned long long best = slot_poll(slot);
           const unsigned long long mine = (best & ~255ull) | epoch;
           for (int p = 1; p <= ka.world; p++) {     // peers first, own mailbox last
             const int q = (ka.rank + p) % ka.world;
@@ -227,13 +232,7 @@ __device__ __forceinline__ void slot_arrive(OpSync* slot, unsigned long long war
   }
 }
 __device__ __forceinline__ unsigned long long slot_wait(OpSync* slot, unsigned long long* s_win) {
-  if (threadIdx.x == 0) {
-    unsigned long long best = 0, cnt;
-    do {
-      asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(best), "=l"(cnt) : "l"(slot) : "memory");
-    } while ((uint32_t)cnt < gridDim.x);
-    *s_win = best;
-  }
+  if (threadIdx.x == 0) *s_win = slot_poll(slot);
   __syncthreads();
   return *s_win;
 }

@@ -1143,13 +1143,14 @@ void Scheduler::AddNode(const NodeInfo& info) {
     nodeIndex_[info.ID] = (int)nodes_.size();
     nodes_.push_back(std::move(ne));
   } else {
+    // the reference rebuilds usage on every Filter by joining the pod cache and the node's devices by UUID
+    // (getNodesUsage, scheduler.go:757-842): a device that left the annotation and came back finds its pods again
     NodeEntry& ne = *nodes_[it->second];
-    for (auto& u : usage)
-      for (auto& old : ne.usage)
-        if (old.ID == u.ID) { u.Used = old.Used; u.Usedmem = old.Usedmem; u.Usedcores = old.Usedcores; }
     ne.info = info;
     ne.usage = usage;
     ne.alive = true;
+    for (auto& kv : pods_)
+      if (kv.second.NodeID == info.ID) applyUsage(ne, kv.second.Devices, +1);
   }
 }
 

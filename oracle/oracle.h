@@ -38,10 +38,9 @@
  *  order (policy/node_policy.go:69 ranges over a map).
  *
  * Not restated (outside the built scope, the oracle refuses such inputs):
- * dynamic MIG placement (nvidia/device.go:602-639, mig_topology.go) and
- * namespace ResourceQuota (device/quota.go) — every BASELINE config runs
- * without either; FitQuota returns true when the namespace has no quota entry
- * (quota.go:73-76).
+ * dynamic MIG placement (nvidia/device.go:602-639, mig_topology.go).
+ * Namespace ResourceQuota IS restated (QuotaManager / fitQuota, device/quota.go:62-150,
+ * nvidia/device.go:666-692, cambricon/device.go:351-376) and pinned on TestFitQuota.
  */
 #ifndef HAMI_ORACLE_H_
 #define HAMI_ORACLE_H_

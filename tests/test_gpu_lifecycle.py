@@ -91,7 +91,14 @@ def test_node_reregisters_with_reordered_and_replaced_devices():
     n1["devices"] = [dict(d, id=d["id"] + "-new") if i == 0 else d for i, d in enumerate(n1["devices"])]   # one card swapped
     o.node_upsert(n1); e.node_upsert(n1)
     assert e.snapshot(n1["name"]) == o.snapshot(n1["name"])
-    run(ops[300:])
+    run(ops[300:350])
+    # the swapped card's original UUID is registered again: the pods that sat on it still hold it (the reference joins
+    # pods and devices by UUID on every rebuild), so its usage is back — no over-commit
+    old0 = n1["devices"][0]["id"][:-len("-new")]
+    n1["devices"] = [dict(d, id=old0) if i == 0 else d for i, d in enumerate(n1["devices"])]
+    o.node_upsert(n1); e.node_upsert(n1)
+    assert e.snapshot(n1["name"]) == o.snapshot(n1["name"])
+    run(ops[350:])
     e.close()
     o.close()
 

@@ -97,3 +97,65 @@ def test_simulation_on_transient_nodes():
             assert got["failed"]["empty-template-%d" % i] == "node unregistered"
     assert {n["name"]: e.snapshot(n["name"]) for n in nodes[:20]} == live_before
     e.close()
+
+
+def test_simulation_keeps_metax_and_neuron_fit_classes():
+    """The transient inventory must judge a vendor with the parent's own Fit class: metax nodes keep their ScoreNode
+    term (2000 - loss / score tables) and customFilterRule, AWS Neuron nodes their core masks and graphSelect."""
+    import k8s_vgpu_scheduler_b200.engine as eng
+    from test_plain_vendors import _metax_cluster, _neuron_cluster
+    checked = 0
+    for make in (_metax_cluster, _neuron_cluster):
+        made = make()
+        cfg, nodes, ops = made[:3]
+        caps = made[3] if len(made) > 3 else {}
+        e = eng.Engine(cfg.get("node_policy"), cfg.get("gpu_policy"))
+        pods = [a for k, a in ops if k == "filter"][:80]
+        for i, pod in enumerate(pods):
+            chosen = [nodes[(i * 5 + j * 3) % len(nodes)] for j in range(2 + i % 5)]
+            chosen = list({n["name"]: n for n in chosen}.values())
+            sim, twins = [], []
+            for n in chosen:
+                if n["devices"][0]["vendor"] == "Metax-GPU":
+                    regs = [("Metax-GPU", abi.HS_REG_CAPACITY_METAX, n.get("metax_losses"), n.get("metax_scores"), None, len(n["devices"]), 0)]
+                elif n["name"] in caps:                      # registered from capacity + instance type: every device healthy
+                    counts, total, itype = caps[n["name"]]
+                    regs = [("AWSNeuron", abi.HS_REG_CAPACITY_NEURON, itype, None, n["name"], counts, total, 0)]
+                    n = dict(n, devices=[dict(d, health=True) for d in n["devices"]])
+                else:
+                    regs = registrations(n)
+                sim.append((n["name"], regs, None, -1))
+                twins.append(n)
+            o = oa.Oracle(cfg.get("node_policy"), cfg.get("gpu_policy"))
+            for n in twins:
+                o.node_upsert(n)
+            ref = o.filter(pod, [s[0] for s in sim])
+            o.close()
+            got = e.filter_simulate(pod, sim)
+            assert same_decision(ref, got), (make.__name__, i, ref, got)
+            checked += ref["status"] == abi.HS_FIT
+        e.close()
+    assert checked > 40
+
+
+def test_simulation_honours_the_namespace_quota():
+    """filterSimulation goes through the same Fit, fitQuota included: a namespace that has used up its quota is
+    refused on transient nodes too, with ResourceQuotaNotFit."""
+    import k8s_vgpu_scheduler_b200.engine as eng
+    import k8s_vgpu_scheduler_b200.gen as gen
+    cfg, nodes, ops = gen.config2(n_nodes=8, n_pods=40)
+    e = eng.Engine(cfg.get("node_policy"), cfg.get("gpu_policy"))
+    for n in nodes[:4]:
+        e.node_upsert(n)
+    pod = dict(next(a for k, a in ops if k == "filter"), ns="tight", uid="q-pod")
+    pod["containers"] = [[{"key": "NVIDIA", "type": "NVIDIA", "nums": 1, "memreq": 4000, "mempct": 101, "coresreq": 10}]]
+    pod["annotations"] = {}
+    sim = [(n["name"], registrations(n), None, -1) for n in nodes[4:]]
+    assert e.filter_simulate(pod, sim)["status"] == abi.HS_FIT
+    e.quota_set("tight", "NVIDIA", 0, 3000)             # less memory than the pod asks for
+    got = e.filter_simulate(pod, sim)
+    assert got["status"] == abi.HS_NOFIT
+    assert all("ResourceQuotaNotFit" in r for r in got["failed"].values()), got["failed"]
+    e.quota_del("tight", "NVIDIA", 0)
+    assert e.filter_simulate(pod, sim)["status"] == abi.HS_FIT
+    e.close()
