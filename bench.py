@@ -39,6 +39,19 @@ WORKLOAD = "c3"
 METRIC = "sched decisions/sec at 5k nodes x 8 GPUs"
 UNIT = "decisions/s"
 
+# BASELINE.json's configs at their stated sizes: nodes, prefill filters (enough to reach the generator's steady
+# occupancy), ops per step, and what the line's config.workload says
+WORKLOADS = {
+    "c1": dict(nodes=4, fill=200, batch=1000, gen=dict(departures=0.3),
+               desc="C1: 4 nodes x 8 x 80 GB, identical 3000 MiB / 30-core pods, binpack/binpack, 30% departures"),
+    "c2": dict(nodes=1000, fill=8000, batch=4096, gen={},
+               desc="C2: 1,000 nodes x 8 x 80 GB, mixed 1-8 GPU pods (gpumem / gpumem-percentage), spread/spread, ~70% occupancy"),
+    "c3": dict(nodes=5000, fill=16000, batch=4096, gen={},
+               desc="C3: 5000 nodes x 8 x 180 GB, NVLink pair scores (20% PCIe nodes), topology-aware 2/4/8-GPU pods, 25% numa-bind, ~70% occupancy"),
+    "c4": dict(nodes=20000, fill=120000, batch=4096, gen={},
+               desc="C4: 20,000 heterogeneous nodes (NVIDIA x4 models / Ascend910B3 / MLU / DCU), type and UUID use/nouse selectors, 2% unhealthy, ~60% occupancy"),
+}
+
 
 def ncpu():
     try:
@@ -111,7 +124,10 @@ def make_stream(steps, warmup, n_nodes, fill_filters, batch_ops):
     import k8s_vgpu_scheduler_b200.gen as gen
     # enough filters for the fill phase plus (warmup + steps) batches; deletes ride along in the stream
     n_pods = fill_filters + (warmup + steps + 1) * batch_ops
-    cfg, nodes, ops = gen.CONFIGS[WORKLOAD](n_nodes=n_nodes, n_pods=n_pods)
+    kw = dict(WORKLOADS.get(WORKLOAD, {}).get("gen", {}))
+    if WORKLOAD != "c1":
+        kw["n_nodes"] = n_nodes
+    cfg, nodes, ops = gen.CONFIGS[WORKLOAD](n_pods=n_pods, **kw)
     # split: fill = prefix holding `fill_filters` filter ops
     cnt, cut = 0, 0
     for i, (k, _) in enumerate(ops):
@@ -123,6 +139,37 @@ def make_stream(steps, warmup, n_nodes, fill_filters, batch_ops):
     fill, rest = ops[:cut], ops[cut:]
     batches = [rest[i * batch_ops:(i + 1) * batch_ops] for i in range(warmup + steps)]
     return cfg, nodes, fill, batches
+
+
+def live_uids(op_lists):
+    """uids filtered and not deleted since, in stream order (whether each one holds devices is the pod cache's business)"""
+    live = {}
+    for ops in op_lists:
+        for kind, arg in ops:
+            if kind == "filter":
+                live[arg["uid"]] = True
+            else:
+                live.pop(arg, None)
+    return list(live)
+
+
+def pod_cache(engine, uids):
+    """podManager's content for `uids` (hs_pod_get): [(uid, node, [(uuid, slots, mem, cores)])]"""
+    out = []
+    for u in uids:
+        got = engine.pod_get(u)
+        if got is not None and got[1]:
+            out.append((u, got[0], got[1]))
+    return out
+
+
+def inject_pods(target, pods, kind):
+    """Recreate a pod cache (and with it the usage of every device) in a fresh oracle / engine, pod by pod, under the
+    pods' own uids — so the deletes of the measured stream release exactly what they release in the timed engine."""
+    for uid, node, rows in pods:
+        for uuid, slots, mem, cores in rows:
+            rc = target.usage_apply(uid, node, uuid, slots, mem, cores)
+            assert rc == 0, (kind, uid, rc)
 
 
 def algorithmic_bytes(ops, n_nodes):
@@ -149,6 +196,40 @@ def decide_traffic():
         return None
 
 
+def pct(xs, q):
+    xs = sorted(xs)
+    if not xs:
+        return None
+    return xs[min(len(xs) - 1, int(q * (len(xs) - 1) + 0.5))]
+
+
+def latency_leg(e, eng, ops, n_filters):
+    """p50 / p99 of ONE Scheduler.Filter (scheduler.go:1067-1154) as an extender sees it: hs_filter per pod, host
+    submit -> result visible (perf_counter around the C-ABI call; the pod struct is marshalled beforehand, as the cgo
+    shim would have it).  Deletes of the stream are applied in between (untimed) so the occupancy holds."""
+    import ctypes as C
+    from k8s_vgpu_scheduler_b200 import abi
+    L = e.L
+    res = abi.hs_filter_result()
+    lat, fits = [], 0
+    for kind, arg in ops:
+        if len(lat) >= n_filters:
+            break
+        if kind != "filter":
+            e.pod_delete(arg)
+            continue
+        p, keep = abi.build_pod(arg)
+        t0 = time.perf_counter()
+        rc = L.hs_filter(e.h, C.byref(p), None, 0, C.byref(res))
+        lat.append(time.perf_counter() - t0)
+        fits += rc == 0
+    us = [1e6 * x for x in lat]
+    return {"calls": len(us), "fits": fits, "p50_us": round(pct(us, 0.50), 1), "p99_us": round(pct(us, 0.99), 1),
+            "max_us": round(max(us), 1), "mean_us": round(statistics.mean(us), 1),
+            "what": "single hs_filter calls (one Scheduler.Filter each: compile, launch, commit, result assembly), host "
+                    "perf_counter submit -> result visible; deletes of the stream applied between calls"}
+
+
 def run_ours(args):
     import torch  # device memory / streams / distributed are torch's job on the multi-GPU path
     import k8s_vgpu_scheduler_b200.engine as eng
@@ -164,30 +245,29 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
     torch.cuda.set_device(local_rank)
 
-    cfg, nodes, fill, batches = make_stream(args.steps, args.warmup, args.nodes, args.fill, args.batch)
+    extra = 3 if not args.no_latency else 0          # batches after the timed ones feed the single-call latency leg
+    cfg, nodes, fill, batches = make_stream(args.steps + extra, args.warmup, args.nodes, args.fill, args.batch)
     e = eng.Engine(cfg["node_policy"], cfg["gpu_policy"], cuda_device=local_rank)
     for n in nodes:
         e.node_upsert(n)
     fill_packed = eng.PackedOps(fill)
-    packed = [eng.PackedOps(b) for b in batches]
+    packed = [eng.PackedOps(b) for b in batches[:args.warmup + args.steps]]
     e.run_batch(fill_packed)
     fill_fit, fill_nofit, _ = e.batch_summary()
-
-    # cluster state at the start of the measured stream, for the CPU baseline / parity sample
-    def snapshot_all(engine):
-        return {n["name"]: engine.snapshot(n["name"]) for n in nodes}
 
     for i in range(args.warmup):
         e.run_batch(packed[i])
         e.batch_summary()
-    state0 = snapshot_all(e) if not args.no_cpu else None
+    # podManager's content at the start of the measured stream, for the CPU baseline / parity sample
+    pods0 = pod_cache(e, live_uids([fill] + batches[:args.warmup])) if not args.no_cpu else None
 
     sampler = ClockSampler(local_rank)
     sampler.start()
     host0 = e.host_seconds()
     launches0 = e.launch_count()
+    bytes0 = e.copy_bytes()
     dev_ms, e2e_s, fits, nofits, decisions, bytes_alg = [], [], 0, 0, 0, 0
-    h2d = d2h = 0
+    gaps_us = []
     torch.cuda.synchronize()
     for i in range(args.warmup, args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -201,13 +281,13 @@ def run_ours(args):
         nfilt = sum(1 for k, _ in batches[i] if k == "filter")
         decisions += nfilt
         bytes_alg += algorithmic_bytes(batches[i], args.nodes)
-        # bytes this step moves over PCIe: request descriptors in, decision records out
-        h2d += len(batches[i]) * 96 + nfilt * 64
-        d2h += len(batches[i]) * (32 + 128) + nf * 4 * 8
+        ts = sorted(t for t in e.decision_ns(len(batches[i])) if t)
+        gaps_us += [(b - a) / 1e3 for a, b in zip(ts, ts[1:])]
     torch.cuda.synchronize()
     clocks = sampler.stop()
     launches = e.launch_count() - launches0
     host1 = e.host_seconds()
+    bytes1 = e.copy_bytes()
     host_ms = [round(1e3 * (b - a) / args.steps, 3) for a, b in zip(host0, host1)]
 
     total_dev_s = sum(dev_ms) / 1e3
@@ -215,19 +295,20 @@ def run_ours(args):
     e2e_val = decisions / sum(e2e_s)
     peak, peak_src = measured_peak()
     achieved = bytes_alg / total_dev_s / 1e9
+    wl = WORKLOADS[WORKLOAD]
     out = {
-        "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+        "metric": METRIC if WORKLOAD == "c3" else "sched decisions/sec on BASELINE config %s (%d nodes x 8)" % (WORKLOAD.upper(), args.nodes),
+        "value": round(value, 1), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(statistics.mean(dev_ms), 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "int32+f32", "data": "synthetic",
-        "config": {"workload": ("C3: %d nodes x 8 x 180 GB, NVLink pair scores (20%% PCIe nodes), topology-aware 2/4/8-GPU "
-                                "pods, 25%% numa-bind, ~70%% occupancy" % args.nodes) if WORKLOAD == "c3" else
-                               "%s stream on %d nodes (diagnostic run, not the headline config)" % (WORKLOAD, args.nodes),
+        "config": {"workload": wl["desc"] if args.nodes == wl["nodes"] else "%s stream on %d nodes (scaled run)" % (WORKLOAD, args.nodes),
                    "ops_per_step": args.batch, "decisions_timed": decisions, "fits": fits, "no_fits": nofits,
                    "prefill_filters": args.fill, "prefill_fits": fill_fit,
                    "l2": "inventory (%.2f MB) is L2/register resident by design; no flush: each decision depends on the "
                          "previous commit" % (args.nodes * 256 / 1e6)},
-        "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": h2d // args.steps,
-                "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": round(1e3 * statistics.mean(e2e_s), 3),
+        "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": int((bytes1[0] - bytes0[0]) // args.steps),
+                "d2h_bytes_per_step": int((bytes1[1] - bytes0[1]) // args.steps), "bytes": "measured at the copies (hs_debug_copy_bytes)",
+                "ms_per_step": round(1e3 * statistics.mean(e2e_s), 3),
                 "host_ms_per_step": {"compile": host_ms[0], "device_and_copies": host_ms[1], "absorb": host_ms[2],
                                      "materialise": host_ms[3]}},
         "gpu_launches": int(launches),
@@ -236,13 +317,22 @@ def run_ours(args):
                      "frac": round(achieved / peak, 4), "traffic": decide_traffic(), "peak_source": peak_src,
                      "kernel": "hs_decide_kernel",
                      "note": "algorithmic bytes = decisions x (N x 8 x 32 B + N x 128 B topology tile + nums x 16 B); "
-                             "at 5k nodes the loop is barrier-latency bound, HBM evidence is the scan probe (profiles/)"},
+                             "the inventory is L2/register resident, HBM evidence is the scan probe (profiles/)"},
     }
+    if gaps_us:
+        out["latency"] = {"in_batch_completion_gap_us": {"p50": round(pct(gaps_us, 0.5), 2), "p99": round(pct(gaps_us, 0.99), 2),
+                                                         "max": round(max(gaps_us), 2),
+                                                         "what": "time between consecutive decisions becoming final on the device inside hs_run_batch (%globaltimer)"}}
+    if not args.no_latency:
+        lat_ops = [op for b in batches[args.warmup + args.steps:] for op in b]
+        out.setdefault("latency", {})["filter"] = latency_leg(e, eng, lat_ops, args.latency_calls)
 
     if not args.no_scan:
         out["scan_hbm"] = scan_probe(args.scan_nodes, peak)
     if not args.no_cpu:
-        out["cpu_baseline"] = cpu_baseline(cfg, nodes, state0, batches[args.warmup], eng, oa, args, local_rank)
+        out["cpu_baseline"] = cpu_baseline(cfg, nodes, pods0, batches[args.warmup], eng, oa, args, local_rank)
+        if "latency" in out and "filter" in out["latency"] and out["cpu_baseline"].get("filter_ms"):
+            out["latency"]["cpu_oracle_filter_ms"] = out["cpu_baseline"].pop("filter_ms")
     e.close()
     print(json.dumps(out))
 
@@ -263,46 +353,50 @@ def scan_probe(n_nodes, peak):
         return {"error": str(ex)}
 
 
-def inject_state(target, nodes, state, kind):
-    """Recreate a usage cache in a fresh oracle / engine: one synthetic pod per busy device."""
-    for n in nodes:
-        rows = state[n["name"]]
-        for d, (used, mem, cores) in zip(n["devices"], rows):
-            if used or mem or cores:
-                rc = target.usage_apply("seed-" + d["id"], n["name"], d["id"], used, mem, cores)
-                assert rc == 0, (kind, rc)
-
-
-def cpu_baseline(cfg, nodes, state0, batch, eng, oa, args, local_rank):
-    filters = [op for op in batch if op[0] == "filter"]
+def cpu_baseline(cfg, nodes, pods0, batch, eng, oa, args, local_rank):
+    """The CPU oracle on a bounded, CONTIGUOUS sample of the first timed batch — filters and deletes — from the very
+    pod cache the timed engine had at that point, and the same sample through a second engine handle: the FNV digest
+    over every result (status, node, score bits, annotation strings, FailedNodes; delete statuses) must be equal."""
     threads = ncpu()
     o = oa.Oracle(cfg["node_policy"], cfg["gpu_policy"], faithful=False, threads=threads)
     for n in nodes:
         o.node_upsert(n)
-    inject_state(o, nodes, state0, "oracle")
-    # size the sample for roughly 10-20 s of CPU work
-    probe = eng.PackedOps(filters[:8])
-    _, _, _, sec = o.run_ops(probe)
-    per = max(sec / 8, 1e-6)
-    s = int(max(16, min(len(filters) - 8, args.cpu_seconds / per)))
-    sample_ops = filters[8:8 + s]
+    inject_pods(o, pods0, "oracle")
+    # size the sample for roughly args.cpu_seconds of CPU work: time a few filters first
+    k = 0
+    nfilt = 0
+    while k < len(batch) and nfilt < 8:
+        nfilt += batch[k][0] == "filter"
+        k += 1
+    probe_ops = batch[:k]
+    _, _, d_probe_o, sec = o.run_ops(eng.PackedOps(probe_ops))
+    per = max(sec / max(nfilt, 1), 1e-6)
+    want = int(max(16, args.cpu_seconds / per))
+    end, nf2 = k, 0
+    while end < len(batch) and nf2 < want:
+        nf2 += batch[end][0] == "filter"
+        end += 1
+    sample_ops = batch[k:end]
     sample = eng.PackedOps(sample_ops)
     nf, nn, digest_o, sec = o.run_ops(sample)
     o.close()
-    # the same sample, from the same state, through a second engine handle: digest parity
+    # the same ops, from the same pod cache, through a second engine handle: digest parity
     e2 = eng.Engine(cfg["node_policy"], cfg["gpu_policy"], cuda_device=local_rank)
     for n in nodes:
         e2.node_upsert(n)
-    inject_state(e2, nodes, state0, "engine")
-    e2.run_batch(probe)
+    inject_pods(e2, pods0, "engine")
+    e2.run_batch(eng.PackedOps(probe_ops))
+    _, _, d_probe_e = e2.batch_summary()
     e2.run_batch(sample)
     gf, gn, digest_e = e2.batch_summary()
     e2.close()
-    return {"value": round(len(sample_ops) / sec, 2), "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": "%d filter ops of the first timed batch from the same cluster state (deletes skipped), oracle in "
-                      "its lean shape (incremental usage, %d threads over node chunks)" % (len(sample_ops), threads),
-            "seconds": round(sec, 2),
-            "parity": {"digest_match": digest_o == digest_e, "fits": [nf, gf], "no_fits": [nn, gn]}}
+    n_del = sum(1 for kk, _ in sample_ops if kk != "filter")
+    return {"value": round(nf2 / sec, 2), "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "%d contiguous ops of the first timed batch (%d filters, %d deletes) from the same pod cache, oracle in "
+                      "its lean shape (incremental usage, %d threads over node chunks)" % (len(sample_ops), nf2, n_del, threads),
+            "seconds": round(sec, 2), "filter_ms": round(1e3 * per, 3),
+            "parity": {"digest_match": digest_o == digest_e and d_probe_o == d_probe_e, "ops": len(sample_ops) + len(probe_ops),
+                       "deletes": n_del, "fits": [nf, gf], "no_fits": [nn, gn]}}
 
 
 def run_reference(args):
@@ -334,12 +428,28 @@ def run_reference(args):
         fill, rest = ops[:cut], ops[cut:]
         batches = [rest[i * step_ops:(i + 1) * step_ops] for i in range(args.warmup + args.steps)]
     else:
+        # the GPU arm's own stream: same prefill, same step boundaries; each timed step is a bounded sample (the first
+        # `step_ops` ops) of that step's 4,096-op batch
         n_nodes = args.nodes
-        cfg, nodes, fill, batches = make_stream(args.steps, args.warmup, args.nodes, prefill, step_ops)
+        prefill = args.fill
+        cfg, nodes, fill, full = make_stream(args.steps, args.warmup, args.nodes, args.fill, args.batch)
+        batches = [b[:step_ops] for b in full]
     o = oa.Oracle(cfg["node_policy"], cfg["gpu_policy"], faithful=False, threads=threads)
     for n in nodes:
         o.node_upsert(n)
-    o.run_ops(eng.PackedOps(fill))           # untimed prefill in the lean shape (it is only state set-up)
+    fixture = os.path.join(ROOT, "tests", "golden", "%s_prefill_pods.json.gz" % WORKLOAD)
+    state_from = "oracle prefill (lean shape, untimed)"
+    loaded = False
+    if not multi and os.path.exists(fixture):
+        import gzip
+        with gzip.open(fixture, "rt") as f:
+            fx = json.load(f)
+        if fx.get("nodes") == n_nodes and fx.get("prefill_filters") == prefill and fx.get("fill_ops") == len(fill):
+            inject_pods(o, [(u, nd, [tuple(r) for r in rows]) for u, nd, rows in fx["pods"]], "oracle")
+            state_from = "pod cache after the same %d prefill filters (tests/golden/%s, written by the oracle itself: tools/make_prefill_fixture.py)" % (prefill, os.path.basename(fixture))
+            loaded = True
+    if not loaded:
+        o.run_ops(eng.PackedOps(fill))       # untimed prefill in the lean shape (it is only state set-up)
     o.L.oracle_set_mode(o.h, 1, threads)     # timed: rebuild usage from the pod cache on every Filter
     packed = [eng.PackedOps(b) for b in batches]
     for i in range(args.warmup):
@@ -351,16 +461,19 @@ def run_reference(args):
         decisions += sum(1 for k, _ in batches[i] if k == "filter")
     o.close()
     value = decisions / sum(secs)
-    sample = ("%d ops per step of the %s stream after %d prefill filters; oracle (C++ restatement of the reference) in "
-              "its faithful shape: usage rebuilt from the whole pod cache per Filter, %d threads over node chunks"
-              % (step_ops, "C5" if multi else "C3", prefill, threads))
-    out = {"impl": "reference", "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": args.gpus,
+    sample = ("the first %d ops of each %d-op step of the %s stream, cluster state: %s; oracle (C++ restatement of the "
+              "reference) in its faithful shape: usage rebuilt from the whole pod cache per Filter, %d threads over node chunks"
+              % (step_ops, step_ops if multi else args.batch, "C5" if multi else WORKLOAD.upper(), state_from, threads))
+    out = {"impl": "reference",
+           "metric": METRIC if (multi or WORKLOAD == "c3") else "sched decisions/sec on BASELINE config %s (%d nodes x 8)" % (WORKLOAD.upper(), n_nodes),
+           "value": round(value, 2), "unit": UNIT, "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * statistics.mean(secs), 3),
            "higher_is_better": True, "scaling": "strong" if multi else "weak", "vs_baseline": None, "dtype": "int32+f32",
            "data": "synthetic",
            "config": {"workload": ("C5: %d-node inventory (C2 device/request mix), one host, no sharding (bounded sample)" % n_nodes) if multi
-                      else ("C3: %d nodes x 8 x 180 GB, topology-aware 2/4/8-GPU pods (bounded sample)" % n_nodes),
-                      "ops_per_step": step_ops},
+                      else WORKLOADS[WORKLOAD]["desc"],
+                      "ops_per_step": step_ops if multi else args.batch, "prefill_filters": prefill,
+                      "sample_ops_per_step": step_ops},
            "cpu_baseline": {"value": round(value, 2), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
            "e2e": {"value": round(value, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0,
@@ -374,20 +487,29 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--nodes", type=int, default=N_NODES)
-    ap.add_argument("--batch", type=int, default=BATCH_OPS)
-    ap.add_argument("--fill", type=int, default=FILL_FILTERS)
+    ap.add_argument("--nodes", type=int, default=None)
+    ap.add_argument("--batch", type=int, default=None)
+    ap.add_argument("--fill", type=int, default=None)
+    ap.add_argument("--no-latency", action="store_true", help="skip the single-call Filter latency leg")
+    ap.add_argument("--latency-calls", type=int, default=10000)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-scan", action="store_true", help="skip the HBM scan probe")
     ap.add_argument("--scan-nodes", type=int, default=2000000)
     ap.add_argument("--ref-ops", type=int, default=96, help="ops per step of the --impl reference arm")
     ap.add_argument("--ref-prefill", type=int, default=1500)
-    ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c4", "c5"],
+    ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3", "c4", "c5"],
                     help="diagnostic: another config's stream (c5 = the multi-GPU workload, runnable on 1 GPU for the scaling base)")
     args = ap.parse_args()
     global WORKLOAD
     WORKLOAD = args.workload
+    wl = WORKLOADS.get(WORKLOAD if WORKLOAD != "c5" else "c3")
+    if args.nodes is None:
+        args.nodes = wl["nodes"] if WORKLOAD != "c5" else N_NODES
+    if args.batch is None:
+        args.batch = wl["batch"]
+    if args.fill is None:
+        args.fill = wl["fill"]
     if args.warmup < 3:
         args.warmup = 3
     if args.impl == "reference":

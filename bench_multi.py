@@ -30,6 +30,93 @@ def partition(n_nodes, world):
     return [(min(n_nodes, r * per), min(n_nodes, (r + 1) * per)) for r in range(world)]
 
 
+METRIC = "sched decisions/sec on the 100k-node inventory sharded over N GPUs"
+
+
+def sharded_mismatches(ops, ref, gathered):
+    """Compare a sharded run with the single-scheduler oracle.  gathered: per rank (pos_base, {op: full result of a fit
+    this rank owns}, {op: FailedNodes of this shard}, {op: (global position, score bits) seen as HS_FIT_REMOTE})."""
+    import parity
+    from k8s_vgpu_scheduler_b200 import abi
+    bad = []
+    for i, ((kind, arg), r) in enumerate(zip(ops, ref)):
+        if kind != "filter":
+            continue
+        owners = [(glo, m[i]) for glo, m, _, _ in gathered if i in m]
+        if r["status"] == abi.HS_FIT:
+            if len(owners) != 1:
+                bad.append("op %d: %d owners" % (i, len(owners)))
+                continue
+            glo, g = owners[0]
+            if (g["node"], glo + g["node_index"], parity.f32bits(g["score"]), g["devices"], g["annotations"]) != \
+               (r["node"], r["node_index"], parity.f32bits(r["score"]), r["devices"], r["annotations"]):
+                bad.append("op %d differs: %r vs %r" % (i, g["node"], r["node"]))
+            for _, _, _, rem in gathered:
+                if i in rem and rem[i] != (r["node_index"], parity.f32bits(r["score"])):
+                    bad.append("op %d remote view differs" % i)
+        elif r["status"] == abi.HS_NOFIT:
+            merged = {}
+            for _, _, nf, _ in gathered:
+                merged.update(nf.get(i, {}))
+            if owners or merged != r["failed"]:
+                bad.append("op %d no-fit differs" % i)
+    return bad
+
+
+def shard_results(e, n_ops):
+    import parity
+    from k8s_vgpu_scheduler_b200 import abi
+    got = [e.batch_get(i) for i in range(n_ops)]
+    mine = {i: g for i, g in enumerate(got) if g["status"] == abi.HS_FIT}
+    nofit = {i: g["failed"] for i, g in enumerate(got) if g["status"] == abi.HS_NOFIT}
+    remote = {i: (g["node_index"], parity.f32bits(g["score"])) for i, g in enumerate(got) if g["status"] == abi.HS_FIT_REMOTE}
+    return mine, nofit, remote
+
+
+def parity_leg(e, eng, dist, cfg, nodes, lo, history, extra_batch, rank, world, seconds):
+    """After the timed steps: one more batch of the stream through the SAME sharded engines (fused path), the first ops
+    of it compared in full — node, global position, score bits, device rows, annotation strings, FailedNodes — with
+    the CPU oracle started from the ranks' gathered pod caches.  Untimed."""
+    import bench as B
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_abi as oa
+    pods_here = B.pod_cache(e, B.live_uids(history))
+    gathered_pods = [None] * world
+    dist.all_gather_object(gathered_pods, pods_here)
+    # bound the sample by the oracle's cost: ~30 us per node per thread
+    per = 30e-6 * len(nodes) / max(B.ncpu(), 1)
+    want = int(max(8, min(256, seconds / per)))
+    end, nf = 0, 0
+    while end < len(extra_batch) and nf < want:
+        nf += extra_batch[end][0] == "filter"
+        end += 1
+    sample = extra_batch[:end]
+    e.run_batch(eng.PackedOps(sample))
+    mine, nofit, remote = shard_results(e, len(sample))
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (lo, mine, nofit, remote))
+    out = None
+    if rank == 0:
+        o = oa.Oracle(cfg["node_policy"], cfg["gpu_policy"], faithful=False, threads=B.ncpu())
+        for n in nodes:
+            o.node_upsert(n)
+        for part in gathered_pods:
+            B.inject_pods(o, part, "oracle")
+        ref = []
+        for kind, arg in sample:
+            if kind == "filter":
+                ref.append(o.filter(arg))
+            else:
+                rc = o.pod_delete(arg)
+                ref.append({"status": rc, "rc": rc})
+        o.close()
+        bad = sharded_mismatches(sample, ref, gathered)
+        out = {"ops": len(sample), "filters": nf, "deletes": len(sample) - nf, "mismatches": len(bad), "digest_match": not bad,
+               "what": "the batch after the timed steps, same sharded engines and path, every field of every decision "
+                       "against the CPU oracle started from the ranks' gathered pod caches", "first": bad[:3]}
+    return out
+
+
 def run(args, world, rank, local_rank):
     import torch
     import torch.distributed as dist
@@ -48,7 +135,7 @@ def run(args, world, rank, local_rank):
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_nodes = args.nodes if args.nodes != B.N_NODES else N_NODES
     batch = min(args.batch, BATCH_OPS)
-    n_pods = FILL_FILTERS + (args.warmup + args.steps + 1) * batch
+    n_pods = FILL_FILTERS + (args.warmup + args.steps + 2) * batch
     cfg, nodes, ops = gen.config5(n_nodes=n_nodes, n_pods=n_pods)
     lo, hi = partition(n_nodes, world)[rank]
 
@@ -71,8 +158,8 @@ def run(args, world, rank, local_rank):
                 cut = i + 1
                 break
     fill, rest = ops[:cut], ops[cut:]
-    batches = [rest[i * batch:(i + 1) * batch] for i in range(args.warmup + args.steps)]
-    packed = [eng.PackedOps(b) for b in batches]
+    batches = [rest[i * batch:(i + 1) * batch] for i in range(args.warmup + args.steps + 1)]
+    packed = [eng.PackedOps(b) for b in batches[:args.warmup + args.steps]]
     e.run_batch(eng.PackedOps(fill))
     for i in range(args.warmup):
         e.run_batch(packed[i])
@@ -110,6 +197,10 @@ def run(args, world, rank, local_rank):
                 "per decision sweep -> NCCL allreduce(MAX,uint64) -> owner commit (HS_SHARD_NCCL=1 baseline)"
     mode_note = ("latency-bound: local slot barrier + one NVLink mailbox round trip per decision" if fused
                  else "latency-bound: 3 kernel launches + one 8-byte NCCL allreduce per decision")
+    parity_out = None
+    if not getattr(args, "no_cpu", False):
+        parity_out = parity_leg(e, eng, dist, cfg, nodes, lo, [fill] + batches[:args.warmup + args.steps],
+                                batches[args.warmup + args.steps], rank, world, getattr(args, "cpu_seconds", 12.0))
     # the scaling base: the SAME inventory and the same batches on ONE GPU (rank 0, unsharded engine), so the line
     # carries its own 1-GPU number for this workload (bench.py --gpus 1 runs C3, the metric's config)
     single = None
@@ -133,7 +224,7 @@ def run(args, world, rank, local_rank):
         peak, peak_src = B.measured_peak()
         bytes_alg = decisions * (n_nodes * 8 * 32)
         out = {
-            "metric": B.METRIC, "value": round(decisions / total_dev_s, 1), "unit": B.UNIT, "n_gpus": world,
+            "metric": METRIC if world > 1 else B.METRIC, "value": round(decisions / total_dev_s, 1), "unit": B.UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * total_dev_s / args.steps, 4),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32+f32", "data": "synthetic",
             "config": {"workload": "C5: %d-node inventory (C2 device/request mix) sharded in contiguous blocks over %d GPUs; "
@@ -142,7 +233,7 @@ def run(args, world, rank, local_rank):
                        "no_fits": int(c[1]) // world, "l2": "each rank's shard (%.1f MB) is L2 resident" % ((hi - lo) * 256 / 1e6)},
             "e2e": {"value": round(decisions / total_e2e_s, 1), "unit": B.UNIT,
                     "h2d_bytes_per_step": batch * 160, "d2h_bytes_per_step": batch * 160},
-            "gpu_launches": int(launches), "clocks": clocks, "single_gpu_same_workload": single,
+            "gpu_launches": int(launches), "clocks": clocks, "single_gpu_same_workload": single, "parity": parity_out,
             "roofline": {"bound": "hbm", "achieved": round(bytes_alg / total_dev_s / 1e9, 1), "peak": peak * world,
                          "unit": "GB/s", "frac": round(bytes_alg / total_dev_s / 1e9 / (peak * world), 4), "traffic": None,
                          "peak_source": peak_src + " x n_gpus", "kernel": "hs_decide_kernel" if fused else "hs_sweep_kernel",

@@ -480,6 +480,17 @@ int32_t hs_quota_memory_factor(hs_handle* h, const char* vendor, int32_t factor)
  * AppContainersOnlyDeviceUsage, once (podManager.UpdatePodDevice).                                           */
 int32_t hs_pod_shrink(hs_handle* h, const char* pod_uid, const hs_kv* annotations, uint32_t n_annotations, uint32_t n_init);
 
+/* podManager.GetPod (pkg/device/pods.go:146-155): what the pod cache holds for one pod — the node it is bound to and,
+ * per device of that node it occupies, the collapsed {slots, memory, cores} the next usage rebuild would add
+ * (scheduler.go:782-785).  Returns the number of rows written (devices with non-zero usage), HS_ERR_NOTFOUND for a pod
+ * the cache does not hold.  `node_name` and the uuid strings belong to the handle (valid until the node changes).
+ * Used by metrics and by parity harnesses that rebuild the same cache in a second scheduler.                       */
+typedef struct hs_pod_usage_row {
+  const char* uuid;
+  int32_t     slots, usedmem, usedcores;
+} hs_pod_usage_row;
+int32_t hs_pod_get(hs_handle* h, const char* pod_uid, const char** node_name, hs_pod_usage_row* rows, uint32_t cap);
+
 /* ---- simulation: Scheduler.filterSimulation, pkg/scheduler/scheduler.go:1088-1090,1156-1199 -----
  * hs_filter_dry: Filter against the handle's inventory that releases nothing, commits nothing and remembers
  * nothing (same result record as hs_filter).
@@ -516,10 +527,14 @@ int32_t hs_sweep_static(hs_handle* h, const hs_pod* pod, void* out_device16, voi
 /* The inventory scan in isolation: compile `pod`, run the sweep-only kernel `iters` times over the
  * whole inventory (no commit); average device ms per sweep, the winning candidate position, its score. */
 int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* ms_avg, int32_t* node_index, float* score);
+/* When each Filter decision of the last hs_run_batch became final on the device (%globaltimer ns; 0 = not a Filter). */
+int32_t hs_debug_decision_ns(hs_handle* h, uint64_t* out, uint32_t cap);
 /* Cumulative SM clocks block 0 spent per phase of the decide loop (needs HS_TIMING=1 at hs_create). */
 int32_t hs_debug_timing(hs_handle* h, unsigned long long out[8]);
 /* Cumulative host seconds: request compile, device run + copies, result absorb, summary. */
 int32_t hs_debug_host_seconds(hs_handle* h, double out[4]);
+/* Cumulative bytes the batch path copied host->device [0] and device->host [1], counted at the copies themselves. */
+int32_t hs_debug_copy_bytes(hs_handle* h, uint64_t out[2]);
 /* The host parser behind hs_node_info.metax_losses / metax_scores on its own (parseMetaxAnnos, metax/device.go:168-183):
  * the table's entry for `index` as hs_node_upsert would store it; 0 for a missing key and for any document error. */
 int64_t hs_debug_metax_table(const char* json, int64_t index);

@@ -88,6 +88,10 @@ class hs_device_usage_row(C.Structure):
     _fields_ = [("used", C.c_int32), ("usedmem", C.c_int32), ("usedcores", C.c_int32)]
 
 
+class hs_pod_usage_row(C.Structure):
+    _fields_ = [("uuid", C.c_char_p), ("slots", C.c_int32), ("usedmem", C.c_int32), ("usedcores", C.c_int32)]
+
+
 class hs_ascend_template(C.Structure):
     _fields_ = [("name", C.c_char_p), ("memory", C.c_int64)]
 

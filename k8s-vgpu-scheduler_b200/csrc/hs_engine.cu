@@ -283,6 +283,7 @@ struct hs_handle {
   DBuf<long long> b_quota;
   hs_handle* sim = nullptr;             // child handle holding the transient inventory of hs_filter_simulate
   bool dry_run = false;                 // set around hs_filter_dry: ops neither release nor commit
+  uint64_t bytes_h2d = 0, bytes_d2h = 0;  // measured host<->device copy volume of the batch path
   size_t n_parked = 0;                  // PodRec::parked entries alive in h->pods
   bool poisoned = false;                // a CUDA call failed while a batch was on the device: HBM and the host mirror may differ
   bool hostprof = false;                // HS_HOSTPROF=1: split the summary time by result kind, printed at hs_destroy
@@ -417,15 +418,29 @@ void mark_dirty(hs_handle* h, int node) {
   h->dirty_hi = std::max(h->dirty_hi, t);
 }
 
+// every byte the batch path moves over PCIe is counted where it is copied (bench.py reports the measured figures)
+inline cudaError_t up(hs_handle* h, void* dst, const void* src, size_t bytes) {
+  h->bytes_h2d += bytes;
+  return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, h->stream);
+}
+inline cudaError_t down(hs_handle* h, void* dst, const void* src, size_t bytes) {
+  h->bytes_d2h += bytes;
+  return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, h->stream);
+}
+inline cudaError_t down_sync(hs_handle* h, void* dst, const void* src, size_t bytes) {
+  h->bytes_d2h += bytes;
+  return cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost);
+}
+
 int flush_inventory(hs_handle* h) {
   if (h->dirty_hi < h->dirty_lo) return HS_OK;
   size_t t0 = (size_t)h->dirty_lo, nt = (size_t)(h->dirty_hi - h->dirty_lo + 1);
   size_t o = t0 * HS_D * HS_TILE, n = nt * HS_D * HS_TILE;
-  CUDA_OK(h, cudaMemcpyAsync(h->d_dyn + o, h->h_dyn.data() + o, n * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
-  CUDA_OK(h, cudaMemcpyAsync(h->d_stat + o, h->h_stat.data() + o, n * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
-  CUDA_OK(h, cudaMemcpyAsync(h->d_tot + t0 * HS_TILE, h->h_tot.data() + t0 * HS_TILE, nt * HS_TILE * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
-  CUDA_OK(h, cudaMemcpyAsync(h->d_flags + t0 * HS_TILE, h->h_flags.data() + t0 * HS_TILE, nt * HS_TILE * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
-  CUDA_OK(h, cudaMemcpyAsync(h->d_pair + t0 * HS_TILE * 64, h->h_pair.data() + t0 * HS_TILE * 64, nt * HS_TILE * 64 * sizeof(int16_t), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, up(h, h->d_dyn + o, h->h_dyn.data() + o, n * sizeof(int4)));
+  CUDA_OK(h, up(h, h->d_stat + o, h->h_stat.data() + o, n * sizeof(int4)));
+  CUDA_OK(h, up(h, h->d_tot + t0 * HS_TILE, h->h_tot.data() + t0 * HS_TILE, nt * HS_TILE * sizeof(int4)));
+  CUDA_OK(h, up(h, h->d_flags + t0 * HS_TILE, h->h_flags.data() + t0 * HS_TILE, nt * HS_TILE * sizeof(uint32_t)));
+  CUDA_OK(h, up(h, h->d_pair + t0 * HS_TILE * 64, h->h_pair.data() + t0 * HS_TILE * 64, nt * HS_TILE * 64 * sizeof(int16_t)));
   CUDA_OK(h, cudaStreamSynchronize(h->stream));  // the pageable host vectors may be resized right after
   h->dirty_lo = 1 << 30;
   h->dirty_hi = -1;
@@ -821,11 +836,11 @@ int device_begin(hs_handle* h, int max_ops, uint32_t alloc_bound) {
     return HS_ERR_CUDA;
   }
   h->sync2_base = max_ops;
-  if (h->have_cand) CUDA_OK(h, cudaMemcpyAsync(h->b_candpos.d, h->b_candpos.h, (size_t)n_nodes * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+  if (h->have_cand) CUDA_OK(h, up(h, h->b_candpos.d, h->b_candpos.h, (size_t)n_nodes * sizeof(int32_t)));
   CUDA_OK(h, cudaMemsetAsync(h->b_dec.d, 0xff, (size_t)max_ops * sizeof(DevDecision), h->stream));
   CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, (size_t)max_ops * 2 * sizeof(OpSync), h->stream));   // [0,n): arg-best slots, [n,2n): quota barriers
   if (!h->quota_rows.empty())
-    CUDA_OK(h, cudaMemcpyAsync(h->b_quota.d, h->b_quota.h, h->quota_rows.size() * 4 * sizeof(long long), cudaMemcpyHostToDevice, h->stream));
+    CUDA_OK(h, up(h, h->b_quota.d, h->b_quota.h, h->quota_rows.size() * 4 * sizeof(long long)));
   const int block = h->block;
   const int maxb = hs_decide_max_blocks(block, h->device);
   if (maxb <= 0) { h->err = "hs_decide_kernel cannot be launched cooperatively on this device"; return HS_ERR_CUDA; }
@@ -843,10 +858,10 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
   const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
   const int n_ops = last;
   const int block = h->block, grid = h->grid_now;
-  if (to.pods > from.pods) CUDA_OK(h, cudaMemcpyAsync(h->b_pods.d + from.pods, h->b_pods.h + from.pods, (to.pods - from.pods) * sizeof(DevPod), cudaMemcpyHostToDevice, h->stream));
-  if (to.entries > from.entries) CUDA_OK(h, cudaMemcpyAsync(h->b_entries.d + from.entries, h->b_entries.h + from.entries, (to.entries - from.entries) * sizeof(DevEntry), cudaMemcpyHostToDevice, h->stream));
-  if (to.uuid > from.uuid) CUDA_OK(h, cudaMemcpyAsync(h->b_uuid.d + from.uuid, h->b_uuid.h + from.uuid, (to.uuid - from.uuid) * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
-  if (to.rel > from.rel) CUDA_OK(h, cudaMemcpyAsync(h->b_rel.d + from.rel, h->b_rel.h + from.rel, (to.rel - from.rel) * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+  if (to.pods > from.pods) CUDA_OK(h, up(h, h->b_pods.d + from.pods, h->b_pods.h + from.pods, (to.pods - from.pods) * sizeof(DevPod)));
+  if (to.entries > from.entries) CUDA_OK(h, up(h, h->b_entries.d + from.entries, h->b_entries.h + from.entries, (to.entries - from.entries) * sizeof(DevEntry)));
+  if (to.uuid > from.uuid) CUDA_OK(h, up(h, h->b_uuid.d + from.uuid, h->b_uuid.h + from.uuid, (to.uuid - from.uuid) * sizeof(uint32_t)));
+  if (to.rel > from.rel) CUDA_OK(h, up(h, h->b_rel.d + from.rel, h->b_rel.h + from.rel, (to.rel - from.rel) * sizeof(int4)));
   CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
   int done = first;
   while (done < n_ops) {
@@ -858,7 +873,7 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
     if (le != cudaSuccess) { h->err = std::string("hs_decide_kernel launch: ") + cudaGetErrorString(le); return HS_ERR_CUDA; }
     h->launches++;
     CUDA_OK(h, cudaEventRecord(h->ev1, h->stream));
-    CUDA_OK(h, cudaMemcpyAsync(h->b_counters.h, h->b_counters.d, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_OK(h, down(h, h->b_counters.h, h->b_counters.d, 8 * sizeof(uint32_t)));
     CUDA_OK(h, cudaStreamSynchronize(h->stream));
     float ms = 0;
     cudaEventElapsedTime(&ms, h->ev0, h->ev1);
@@ -869,13 +884,13 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
     if (nfail) {
       size_t base = h->fail_host.size();
       h->fail_host.resize(base + (size_t)nfail * n_nodes);
-      CUDA_OK(h, cudaMemcpyAsync(h->b_fail.h, h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail), cudaMemcpyDeviceToHost, h->stream));
+      CUDA_OK(h, down(h, h->b_fail.h, h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail)));
       CUDA_OK(h, cudaStreamSynchronize(h->stream));
       memcpy(h->fail_host.data() + base, h->b_fail.h, (size_t)nfail * n_nodes * sizeof(DevFail));
     }
     if (ran == 0 && nfail == 0 && n_ops - done > 0) { h->err = "decide kernel made no progress"; return HS_ERR_CUDA; }
     // decisions of this launch
-    CUDA_OK(h, cudaMemcpy(h->b_dec.h + done, h->b_dec.d + done, (size_t)ran * sizeof(DevDecision), cudaMemcpyDeviceToHost));
+    CUDA_OK(h, down_sync(h, h->b_dec.h + done, h->b_dec.d + done, (size_t)ran * sizeof(DevDecision)));
     uint32_t slot_base = (uint32_t)(h->fail_host.size() / std::max(n_nodes, 1)) - nfail;
     for (uint32_t i = 0; i < ran; i++) {
       DevDecision& d = h->b_dec.h[done + i];
@@ -886,7 +901,7 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
       // resume: keep the alloc cursor, clear the fail cursor
       h->b_counters.h[1] = 0; h->b_counters.h[2] = 0; h->b_counters.h[3] = 0; h->b_counters.h[5] = 0;
       CUDA_OK(h, cudaMemsetAsync(h->b_best.d + done, 0, sizeof(OpSync), h->stream));  // op `done` runs again
-      CUDA_OK(h, cudaMemcpyAsync(h->b_counters.d, h->b_counters.h, 8 * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+      CUDA_OK(h, up(h, h->b_counters.d, h->b_counters.h, 8 * sizeof(uint32_t)));
     }
   }
   // (allocation rows sit at each op's own alloc_base, a host-made prefix sum, not behind a device cursor)
@@ -894,8 +909,8 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
 }
 
 int device_end(hs_handle* h, int n_ops, uint32_t alloc_cap) {
-  if (alloc_cap) CUDA_OK(h, cudaMemcpy(h->b_alloc.h, h->b_alloc.d, (size_t)alloc_cap * sizeof(DevAlloc), cudaMemcpyDeviceToHost));
-  CUDA_OK(h, cudaMemcpy(h->b_delta.h, h->b_delta.d, (size_t)n_ops * HS_D * sizeof(int4), cudaMemcpyDeviceToHost));
+  if (alloc_cap) CUDA_OK(h, down_sync(h, h->b_alloc.h, h->b_alloc.d, (size_t)alloc_cap * sizeof(DevAlloc)));
+  CUDA_OK(h, down_sync(h, h->b_delta.h, h->b_delta.d, (size_t)n_ops * HS_D * sizeof(int4)));
   return HS_OK;
 }
 
@@ -938,10 +953,10 @@ int run_device_ops_sharded(hs_handle* h, int n_ops, size_t n_entries, size_t n_u
     h->err = "out of device memory for batch buffers";
     return HS_ERR_CUDA;
   }
-  CUDA_OK(h, cudaMemcpyAsync(h->b_pods.d, h->b_pods.h, (size_t)n_ops * sizeof(DevPod), cudaMemcpyHostToDevice, h->stream));
-  if (n_entries) CUDA_OK(h, cudaMemcpyAsync(h->b_entries.d, h->b_entries.h, n_entries * sizeof(DevEntry), cudaMemcpyHostToDevice, h->stream));
-  if (n_uuid) CUDA_OK(h, cudaMemcpyAsync(h->b_uuid.d, h->b_uuid.h, n_uuid * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
-  if (n_rel) CUDA_OK(h, cudaMemcpyAsync(h->b_rel.d, h->b_rel.h, n_rel * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+  CUDA_OK(h, up(h, h->b_pods.d, h->b_pods.h, (size_t)n_ops * sizeof(DevPod)));
+  if (n_entries) CUDA_OK(h, up(h, h->b_entries.d, h->b_entries.h, n_entries * sizeof(DevEntry)));
+  if (n_uuid) CUDA_OK(h, up(h, h->b_uuid.d, h->b_uuid.h, n_uuid * sizeof(uint32_t)));
+  if (n_rel) CUDA_OK(h, up(h, h->b_rel.d, h->b_rel.h, n_rel * sizeof(int4)));
   CUDA_OK(h, cudaMemsetAsync(h->b_dec.d, 0xff, (size_t)n_ops * sizeof(DevDecision), h->stream));
   CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, (size_t)n_ops * sizeof(OpSync), h->stream));
   CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
@@ -973,21 +988,21 @@ int run_device_ops_sharded(hs_handle* h, int n_ops, size_t n_entries, size_t n_u
     if (le != cudaSuccess) { h->err = std::string("sharded launch: ") + cudaGetErrorString(le); return HS_ERR_CUDA; }
   }
   CUDA_OK(h, cudaEventRecord(h->ev1, h->stream));
-  CUDA_OK(h, cudaMemcpyAsync(h->b_counters.h, h->b_counters.d, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
-  CUDA_OK(h, cudaMemcpyAsync(h->b_dec.h, h->b_dec.d, (size_t)n_ops * sizeof(DevDecision), cudaMemcpyDeviceToHost, h->stream));
-  CUDA_OK(h, cudaMemcpyAsync(h->b_delta.h, h->b_delta.d, (size_t)n_ops * HS_D * sizeof(int4), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_OK(h, down(h, h->b_counters.h, h->b_counters.d, 8 * sizeof(uint32_t)));
+  CUDA_OK(h, down(h, h->b_dec.h, h->b_dec.d, (size_t)n_ops * sizeof(DevDecision)));
+  CUDA_OK(h, down(h, h->b_delta.h, h->b_delta.d, (size_t)n_ops * HS_D * sizeof(int4)));
   CUDA_OK(h, cudaStreamSynchronize(h->stream));
   float ms = 0;
   cudaEventElapsedTime(&ms, h->ev0, h->ev1);
   h->last_ms = ms;
   const uint32_t nalloc = std::min(h->b_counters.h[0], alloc_cap);
-  if (nalloc) CUDA_OK(h, cudaMemcpy(h->b_alloc.h, h->b_alloc.d, (size_t)nalloc * sizeof(DevAlloc), cudaMemcpyDeviceToHost));
+  if (nalloc) CUDA_OK(h, down_sync(h, h->b_alloc.h, h->b_alloc.d, (size_t)nalloc * sizeof(DevAlloc)));
   const uint32_t nfail = std::min(h->b_counters.h[1], shard_fail_cap);
   h->fail_host.clear();
   h->op_fail_slot.assign(n_ops, 0xffffffffu);
   if (nfail) {
     h->fail_host.resize((size_t)nfail * n_nodes);
-    CUDA_OK(h, cudaMemcpy(h->fail_host.data(), h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail), cudaMemcpyDeviceToHost));
+    CUDA_OK(h, down_sync(h, h->fail_host.data(), h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail)));
   }
   for (int op = 0; op < n_ops; op++) {
     const DevDecision& d = h->b_dec.h[op];
@@ -1853,6 +1868,22 @@ int32_t hs_pod_delete(hs_handle* h, const char* pod_uid) {
 
 int32_t hs_rollback(hs_handle* h, const char* pod_uid) { return hs_pod_delete(h, pod_uid); }
 
+int32_t hs_pod_get(hs_handle* h, const char* pod_uid, const char** node_name, hs_pod_usage_row* rows, uint32_t cap) {
+  if (!h || !pod_uid) return HS_ERR_INVALID;
+  auto it = h->pods.find(pod_uid);
+  if (it == h->pods.end()) return HS_ERR_NOTFOUND;
+  const NodeSlot& ns = h->nodes[it->second.node];
+  if (node_name) *node_name = ns.name.c_str();
+  uint32_t n = 0;
+  for (size_t d = 0; d < ns.devs.size() && d < (size_t)HS_D; d++) {
+    const int4& v = it->second.delta[d];
+    if (!(v.x | v.y | v.z)) continue;
+    if (rows && n < cap) rows[n] = hs_pod_usage_row{ns.devs[d].uuid.c_str(), v.x, v.y, v.z};
+    n++;
+  }
+  return (int32_t)n;
+}
+
 int32_t hs_filter(hs_handle* h, const hs_pod* pod, const char* const* node_names, uint32_t n_names,
                   hs_filter_result* out) {
   if (!h || !pod || !out) return HS_ERR_INVALID;
@@ -2076,6 +2107,12 @@ int64_t hs_debug_metax_table(const char* json, int64_t index) {
   return 0;
 }
 
+int32_t hs_debug_copy_bytes(hs_handle* h, uint64_t out[2]) {
+  if (!h) return HS_ERR_INVALID;
+  out[0] = h->bytes_h2d; out[1] = h->bytes_d2h;
+  return HS_OK;
+}
+
 int32_t hs_debug_host_seconds(hs_handle* h, double out[4]) {
   if (!h) return HS_ERR_INVALID;
   for (int i = 0; i < 4; i++) out[i] = h->host_s[i];
@@ -2162,6 +2199,21 @@ int32_t hs_debug_timing(hs_handle* h, unsigned long long out[8]) {
   if (cudaMemcpy(h->b_timing.h, h->b_timing.d, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) return HS_ERR_CUDA;
   for (int i = 0; i < 8; i++) out[i] = h->b_timing.h[i];
   return HS_OK;
+}
+
+/* Diagnostic: when each FILTER decision of the last batch became final on the device — %globaltimer nanoseconds,
+ * one per caller op (0 for ops that are not Filters or never reached the device). */
+int32_t hs_debug_decision_ns(hs_handle* h, uint64_t* out, uint32_t cap) {
+  if (!h || !out) return HS_ERR_INVALID;
+  uint32_t n = 0;
+  for (size_t i = 0; i < h->user_first_op.size() && n < cap; i++, n++) {
+    out[n] = 0;
+    const int op = h->user_first_op[i];
+    if (op < 0 || h->metas[op].kind != OP_FILTER || h->metas[op].status != HS_OK) continue;
+    const DevDecision& d = h->b_dec.h[op];
+    if (d.status == 0 || d.status == 1 || d.status == 3) out[n] = ((uint64_t)d.pad[1] << 32) | d.pad[0];
+  }
+  return (int32_t)n;
 }
 
 double hs_last_device_ms(const hs_handle* h) { return h ? h->last_ms : 0.0; }

@@ -257,6 +257,14 @@ __device__ __forceinline__ void prefetch_wait_oldest() { asm volatile("cp.async.
 
 #define FULL 0xffffffffu
 
+// wall-clock stamp of a decision (ns, %globaltimer): rides in DevDecision::pad so the host can report when each
+// decision of a batch became final (bench.py's latency object)
+__device__ __forceinline__ void stamp_decision(DevDecision& dec) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  dec.pad[0] = (uint32_t)t; dec.pad[1] = (uint32_t)(t >> 32);
+}
+
 extern "C" __global__ void __launch_bounds__(512, 1)
 hs_decide_kernel(const KernelArgs ka) {
   __shared__ __align__(16) DevPod s_op[HS_PF];
@@ -491,7 +499,7 @@ hs_decide_kernel(const KernelArgs ka) {
           if (spread) u = ~u;
           u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
           dec.score = __uint_as_float(u);
-          dec.pad[0] = dec.pad[1] = 0;
+          stamp_decision(dec);
           ka.decisions[r] = dec;
         }
       }
@@ -533,7 +541,7 @@ hs_decide_kernel(const KernelArgs ka) {
           if (glane == 0) {
             DevDecision dec;
             dec.status = 0; dec.node = my_node; dec.score = my_score; dec.alloc_off = off; dec.n_alloc = (uint32_t)np;
-            dec.fail_slot = 0xffffffffu; dec.pad[0] = dec.pad[1] = 0;
+            dec.fail_slot = 0xffffffffu; stamp_decision(dec);
             ka.decisions[r] = dec;
           }
           if (!dry) {
@@ -555,7 +563,7 @@ hs_decide_kernel(const KernelArgs ka) {
           for (int d = 0; d < HS_D; d++) ka.commit_delta[(size_t)r * HS_D + d] = delta[d];
           DevDecision dec;
           dec.status = 0; dec.node = my_node; dec.score = my_score; dec.alloc_off = off; dec.n_alloc = my_nalloc;
-          dec.fail_slot = 0xffffffffu; dec.pad[0] = dec.pad[1] = 0;
+          dec.fail_slot = 0xffffffffu; stamp_decision(dec);
           ka.decisions[r] = dec;
         }
         __syncwarp(gmask);       // lane 0's stores to the slot rows precede the group's reload
@@ -608,7 +616,7 @@ hs_decide_kernel(const KernelArgs ka) {
       if (gtid == 0) {
         DevDecision dec;
         dec.status = 1; dec.node = -1; dec.score = 0.0f; dec.alloc_off = 0; dec.n_alloc = 0;
-        dec.fail_slot = fail_count; dec.pad[0] = dec.pad[1] = 0;
+        dec.fail_slot = fail_count; stamp_decision(dec);
         ka.decisions[r] = dec;
       }
       fail_count++;

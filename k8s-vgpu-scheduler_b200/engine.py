@@ -17,7 +17,7 @@ _lib = None
 EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_batch_get", "hs_rollback",
-    "hs_snapshot_node", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
+    "hs_snapshot_node", "hs_pod_get", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
     "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect",
     "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_filter_dry", "hs_filter_simulate", "hs_quota_set", "hs_quota_del", "hs_quota_get", "hs_quota_memory_factor", "hs_generate_requests", "hs_debug_timing", "hs_debug_host_seconds", "hs_debug_divcheck", "hs_debug_metax_table",
 ]
@@ -52,6 +52,7 @@ def lib():
     L.hs_shard_init.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64]
     L.hs_rollback.argtypes = [C.c_void_p, C.c_char_p]
     L.hs_snapshot_node.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_device_usage_row), C.c_uint32]
+    L.hs_pod_get.argtypes = [C.c_void_p, C.c_char_p, P(C.c_char_p), P(abi.hs_pod_usage_row), C.c_uint32]
     L.hs_decode_node_devices.argtypes = [P(abi.hs_vendor_registration), P(P(abi.hs_device_info)), P(C.c_uint32), P(P(C.c_int32))]
     L.hs_decode_pod_devices.argtypes = [P(abi.hs_kv), C.c_uint32, P(abi.hs_kv), C.c_uint32, P(P(abi.hs_pod_device)), P(C.c_uint32)]
     L.hs_collapse_pod_devices.argtypes = [C.c_int32, C.c_uint32, P(abi.hs_pod_device), C.c_uint32, P(P(abi.hs_pod_device)), P(C.c_uint32)]
@@ -323,6 +324,29 @@ class Engine:
         if n < 0:
             raise RuntimeError("snapshot failed: %d %s" % (n, self.error()))
         return [(rows[i].used, rows[i].usedmem, rows[i].usedcores) for i in range(min(n, cap))]
+
+    def pod_get(self, uid):
+        """podManager.GetPod: (node name, [(uuid, slots, usedmem, usedcores)]) or None when the cache does not hold the pod."""
+        rows = (abi.hs_pod_usage_row * 16)()
+        node = C.c_char_p()
+        n = self.L.hs_pod_get(self.h, abi._b(uid), C.byref(node), rows, 16)
+        if n < 0:
+            return None
+        return node.value.decode(), [(rows[i].uuid.decode(), rows[i].slots, rows[i].usedmem, rows[i].usedcores) for i in range(n)]
+
+    def decision_ns(self, n):
+        """%globaltimer ns at which each Filter decision of the last run_batch became final (0 = not a Filter)."""
+        out = (C.c_uint64 * max(n, 1))()
+        self.L.hs_debug_decision_ns.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_uint32]
+        k = self.L.hs_debug_decision_ns(self.h, out, n)
+        return [out[i] for i in range(max(k, 0))]
+
+    def copy_bytes(self):
+        """cumulative (host->device, device->host) bytes of the batch path, counted at the copies"""
+        out = (C.c_uint64 * 2)()
+        self.L.hs_debug_copy_bytes.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        self.L.hs_debug_copy_bytes(self.h, out)
+        return out[0], out[1]
 
     def host_seconds(self):
         """cumulative host seconds: (request compile, device run + copies, absorb, materialise)"""

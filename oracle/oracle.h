@@ -226,6 +226,7 @@ class Scheduler {
 
   // nodeManager.addNode / rmNodeDevices (nodes.go:76-148)
   void AddNode(const NodeInfo& info);
+  const PodInfo* GetPod(const std::string& uid) const { auto it = pods_.find(uid); return it == pods_.end() ? nullptr : &it->second; }
   bool RemoveNode(const std::string& name);
   // podManager.AddPod fed by the informer (pods.go:57-97)
   bool UsageApply(const std::string& uid, const std::string& node, const std::string& uuid,

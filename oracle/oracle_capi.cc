@@ -1,6 +1,7 @@
 // oracle_capi.cc — TEST INFRASTRUCTURE ONLY.  ctypes-facing wrapper over oracle.cc.
 #include "oracle_capi.h"
 
+#include <array>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -165,6 +166,29 @@ int32_t oracle_usage_apply(oracle_handle* o, const char* pod_uid, const char* no
   return o->s->UsageApply(str(pod_uid), str(node), str(uuid), slots, usedmem, usedcores) ? HS_OK : HS_ERR_NOTFOUND;
 }
 int32_t oracle_pod_delete(oracle_handle* o, const char* pod_uid) { return o->s->DeletePod(str(pod_uid)) ? HS_OK : HS_ERR_NOTFOUND; }
+
+int32_t oracle_pod_get(oracle_handle* o, const char* pod_uid, const char** node_name, hs_pod_usage_row* rows, uint32_t cap) {
+  const PodInfo* pi = o->s->GetPod(str(pod_uid));
+  if (!pi) return HS_ERR_NOTFOUND;
+  Arena& a = o->arena;
+  a.clear();
+  if (node_name) *node_name = a.s(pi->NodeID);
+  std::vector<std::pair<std::string, std::array<int32_t, 3>>> per;   // by UUID, first-seen order
+  for (auto& kv : pi->Devices)
+    for (auto& ctr : kv.second)
+      for (auto& d : ctr) {
+        size_t k = 0;
+        while (k < per.size() && per[k].first != d.UUID) k++;
+        if (k == per.size()) per.push_back({d.UUID, {0, 0, 0}});
+        per[k].second[0] += std::max(d.Slots, 1); per[k].second[1] += d.Usedmem; per[k].second[2] += d.Usedcores;
+      }
+  uint32_t n = 0;
+  for (auto& r : per) {
+    if (rows && n < cap) rows[n] = hs_pod_usage_row{a.s(r.first), r.second[0], r.second[1], r.second[2]};
+    n++;
+  }
+  return (int32_t)n;
+}
 
 int32_t oracle_filter(oracle_handle* o, const hs_pod* pod, const char* const* node_names, uint32_t n_names,
                       hs_filter_result* out) {

@@ -38,6 +38,9 @@ int32_t oracle_node_remove(oracle_handle* o, const char* name);
 int32_t oracle_usage_apply(oracle_handle* o, const char* pod_uid, const char* node, const char* uuid,
                            int32_t slots, int32_t usedmem, int32_t usedcores);
 int32_t oracle_pod_delete(oracle_handle* o, const char* pod_uid);
+/* podManager.GetPod (pods.go:146-155): node and collapsed per-device usage of one cached pod, summed per UUID;
+ * returns the number of rows or HS_ERR_NOTFOUND.  Strings are valid until the next call. */
+int32_t oracle_pod_get(oracle_handle* o, const char* pod_uid, const char** node_name, hs_pod_usage_row* rows, uint32_t cap);
 int32_t oracle_filter(oracle_handle* o, const hs_pod* pod, const char* const* node_names, uint32_t n_names,
                       hs_filter_result* out);
 int32_t oracle_snapshot_node(oracle_handle* o, const char* node, hs_device_usage_row* rows, uint32_t cap);

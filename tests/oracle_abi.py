@@ -43,6 +43,7 @@ def lib():
     L.oracle_node_remove.argtypes = [C.c_void_p, C.c_char_p]
     L.oracle_usage_apply.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.c_int32]
     L.oracle_pod_delete.argtypes = [C.c_void_p, C.c_char_p]
+    L.oracle_pod_get.argtypes = [C.c_void_p, C.c_char_p, P(C.c_char_p), P(abi.hs_pod_usage_row), C.c_uint32]
     L.oracle_filter.argtypes = [C.c_void_p, P(abi.hs_pod), P(C.c_char_p), C.c_uint32, P(abi.hs_filter_result)]
     L.oracle_snapshot_node.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_device_usage_row), C.c_uint32]
     L.oracle_run_ops.argtypes = [C.c_void_p, P(abi.hs_op), C.c_uint32, P(C.c_uint32), P(C.c_uint32), P(C.c_uint64),
@@ -129,6 +130,14 @@ class Oracle:
 
     def pod_delete(self, uid):
         return self.L.oracle_pod_delete(self.h, abi._b(uid))
+
+    def pod_get(self, uid):
+        rows = (abi.hs_pod_usage_row * 16)()
+        node = C.c_char_p()
+        n = self.L.oracle_pod_get(self.h, abi._b(uid), C.byref(node), rows, 16)
+        if n < 0:
+            return None
+        return node.value.decode(), [(rows[i].uuid.decode(), rows[i].slots, rows[i].usedmem, rows[i].usedcores) for i in range(n)]
 
     def filter(self, pod, node_names=None):
         p, keep = abi.build_pod(pod)

@@ -54,28 +54,7 @@ def main():
         dist.all_gather_object(gathered, (lo, mine, nofit, remote))
         if rank == 0:
             ref, _ = parity.run_oracle(cfg, nodes, ops, snapshot=False)
-            bad = []
-            for i, ((kind, arg), r) in enumerate(zip(ops, ref)):
-                if kind != "filter":
-                    continue
-                owners = [(glo, m[i]) for glo, m, _, _ in gathered if i in m]
-                if r["status"] == abi.HS_FIT:
-                    if len(owners) != 1:
-                        bad.append("op %d: %d owners" % (i, len(owners)))
-                        continue
-                    glo, g = owners[0]
-                    if (g["node"], glo + g["node_index"], parity.f32bits(g["score"]), g["devices"], g["annotations"]) != \
-                       (r["node"], r["node_index"], parity.f32bits(r["score"]), r["devices"], r["annotations"]):
-                        bad.append("op %d differs: %r vs %r" % (i, g["node"], r["node"]))
-                    for _, _, _, rem in gathered:
-                        if i in rem and rem[i] != (r["node_index"], parity.f32bits(r["score"])):
-                            bad.append("op %d remote view differs" % i)
-                elif r["status"] == abi.HS_NOFIT:
-                    merged = {}
-                    for _, _, nf, _ in gathered:
-                        merged.update(nf.get(i, {}))
-                    if owners or merged != r["failed"]:
-                        bad.append("op %d no-fit differs" % i)
+            bad = bench_multi.sharded_mismatches(ops, ref, gathered)
             print("shard parity %-3s world %d: %d ops, %d mismatches %s" % (name, world, len(ops), len(bad), bad[:3]))
             bad_total += len(bad)
         e.close()
