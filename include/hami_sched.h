@@ -531,6 +531,9 @@ int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* 
 int32_t hs_debug_decision_ns(hs_handle* h, uint64_t* out, uint32_t cap);
 /* Cumulative SM clocks block 0 spent per phase of the decide loop (needs HS_TIMING=1 at hs_create). */
 int32_t hs_debug_timing(hs_handle* h, unsigned long long out[8]);
+/* All 16 phase clocks (8..11: inside the windows) and the window counters: windows, ops decided in windows, stops on a
+ * no-fit op, stops on a full tracker, winners loaded in the middle of a window. */
+int32_t hs_debug_window_stats(hs_handle* h, unsigned long long timing16[16], uint32_t stats8[8]);
 /* Cumulative host seconds: request compile, device run + copies, result absorb, summary. */
 int32_t hs_debug_host_seconds(hs_handle* h, double out[4]);
 /* Cumulative bytes the batch path copied host->device [0] and device->host [1], counted at the copies themselves. */

@@ -245,6 +245,11 @@ struct hs_handle {
   DBuf<DevFail> b_fail;
   DBuf<uint32_t> b_counters;
   DBuf<int32_t> b_candpos;
+  // windows (hs_window.cuh): per-tile sorted keys / per-op fit masks / heads, sized with the inventory
+  unsigned long long* w_skey = nullptr; uint32_t* w_rmask = nullptr; unsigned long long* w_head = nullptr; uint8_t* w_rank = nullptr;
+  uint32_t* w_stats = nullptr;
+  int w_cap_nodes = 0;
+  bool windows = true;                 // HS_NO_WINDOW=1: every op takes the one-op path (A/B runs, tests)
   DBuf<unsigned long long> b_timing;   // HS_TIMING=1: phase clocks of block 0
   bool timing = false;
   // sharded mode (one process per GPU): contiguous node block per rank, NCCL allreduce-max of the packed key per decision
@@ -810,6 +815,11 @@ int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_ca
   ka.xresult = h->d_mbox ? h->d_mbox + 32 : nullptr;
   ka.xerror = h->d_mbox ? reinterpret_cast<uint32_t*>(h->d_mbox + 36) : nullptr;
   ka.epoch_base = h->epoch_base;
+  // windows: one GPU, the whole inventory as candidates, 256-thread CTAs (a quarter warp per tracked node)
+  const bool win = h->windows && h->w_skey && h->shard_world <= 1 && !h->force_shard && !h->have_cand && h->block == 256 &&
+                   ka.n_nodes <= h->w_cap_nodes && ka.n_nodes / HS_TILE <= HS_WMAX_TILES;
+  ka.w_skey = win ? h->w_skey : nullptr;
+  ka.w_rmask = h->w_rmask; ka.w_head = h->w_head; ka.w_rank = h->w_rank; ka.w_stats = h->w_stats;
   return HS_OK;
 }
 
@@ -834,6 +844,16 @@ int device_begin(hs_handle* h, int max_ops, uint32_t alloc_bound) {
       !h->b_best.ensure((size_t)max_ops * 2) || !h->b_counters.ensure(8) || !h->b_fail.ensure((size_t)h->fail_cap_now * std::max(n_nodes, HS_TILE))) {
     h->err = "out of device memory for batch buffers";
     return HS_ERR_CUDA;
+  }
+  if (h->windows && h->w_cap_nodes < n_nodes && n_nodes / HS_TILE <= HS_WMAX_TILES) {
+    if (h->w_skey) { cudaFree(h->w_skey); cudaFree(h->w_rmask); cudaFree(h->w_head); cudaFree(h->w_rank); h->w_skey = nullptr; }
+    const size_t cap = (size_t)std::max(n_nodes, HS_TILE), tiles = cap / HS_TILE;
+    if (!h->w_stats) { CUDA_OK(h, cudaMalloc(&h->w_stats, 8 * sizeof(uint32_t))); CUDA_OK(h, cudaMemset(h->w_stats, 0, 8 * sizeof(uint32_t))); }
+    CUDA_OK(h, cudaMalloc(&h->w_skey, cap * sizeof(unsigned long long)));
+    CUDA_OK(h, cudaMalloc(&h->w_rmask, tiles * HS_WIN * sizeof(uint32_t)));
+    CUDA_OK(h, cudaMalloc(&h->w_head, tiles * HS_WIN * sizeof(unsigned long long)));
+    CUDA_OK(h, cudaMalloc(&h->w_rank, cap));
+    h->w_cap_nodes = (int)cap;
   }
   h->sync2_base = max_ops;
   if (h->have_cand) CUDA_OK(h, up(h, h->b_candpos.d, h->b_candpos.h, (size_t)n_nodes * sizeof(int32_t)));
@@ -901,6 +921,7 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
       // resume: keep the alloc cursor, clear the fail cursor
       h->b_counters.h[1] = 0; h->b_counters.h[2] = 0; h->b_counters.h[3] = 0; h->b_counters.h[5] = 0;
       CUDA_OK(h, cudaMemsetAsync(h->b_best.d + done, 0, sizeof(OpSync), h->stream));  // op `done` runs again
+      CUDA_OK(h, cudaMemsetAsync(h->b_best.d + h->sync2_base + done, 0, sizeof(OpSync), h->stream));   // … and so may a window that starts there
       CUDA_OK(h, up(h, h->b_counters.d, h->b_counters.h, 8 * sizeof(uint32_t)));
     }
   }
@@ -1346,6 +1367,27 @@ void absorb_results(hs_handle* h, int n_ops) {
   }
 }
 
+// DevPod::win_len for the ops [first, end): how many ops from each one on the decide kernel may take as ONE window
+// (hs_window.cuh).  A window holds common-shape Filters (the register-resident fast path, no dry run) that share the node
+// policy's direction, and releases of namespaces without a quota; it must contain a Filter within its first HS_WIN ops.
+void mark_windows(std::vector<DevPod>& pods, size_t first) {
+  const size_t end = pods.size();
+  int next_len = 0, next_spread = -1, filter_in = 1 << 20;   // state of the run that starts at i+1
+  for (size_t i = end; i-- > first;) {
+    DevPod& p = pods[i];
+    int kind = 0;                                             // 0 not eligible, 1 filter, 2 release / nop
+    if (p.op == OP_FILTER) kind = (p.fast && !(p.flags & PF_DRYRUN)) ? 1 : 0;
+    else if (p.op == OP_RELEASE) kind = (p.q_idx[0] < 0 && p.q_idx[1] < 0) ? 2 : 0;
+    else kind = 2;
+    if (!kind) { p.win_len = 0; next_len = 0; next_spread = -1; filter_in = 1 << 20; continue; }
+    const int my_spread = kind == 1 ? ((p.flags & PF_NODE_SPREAD) ? 1 : 0) : -1;
+    if (kind == 1 && next_spread >= 0 && next_spread != my_spread) { next_len = 0; filter_in = 1 << 20; }   // the direction changes: the run ends here
+    next_len = std::min(255, next_len + 1);
+    if (kind == 1) { next_spread = my_spread; filter_in = 0; } else filter_in = std::min(filter_in + 1, 1 << 20);
+    p.win_len = filter_in < HS_WIN ? (uint8_t)next_len : (uint8_t)0;
+  }
+}
+
 // Compile caller ops into device ops (implicit release of a pod that is filtered again,
 // scheduler.go:1092-1094), run them, absorb the results.
 static inline double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
@@ -1414,6 +1456,7 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
     if (h->b_entries.cap != ce) { staged.entries = 0; mark.entries = 0; }
     if (h->b_uuid.cap != cu) { staged.uuid = 0; mark.uuid = 0; }
     if (h->b_rel.cap != cr) { staged.rel = 0; mark.rel = 0; }
+    mark_windows(pods, staged.pods);
     memcpy(h->b_pods.h + staged.pods, pods.data() + staged.pods, (pods.size() - staged.pods) * sizeof(DevPod));
     if (entries.size() > staged.entries) memcpy(h->b_entries.h + staged.entries, entries.data() + staged.entries, (entries.size() - staged.entries) * sizeof(DevEntry));
     if (uuid_pool.size() > staged.uuid) memcpy(h->b_uuid.h + staged.uuid, uuid_pool.data() + staged.uuid, (uuid_pool.size() - staged.uuid) * sizeof(uint32_t));
@@ -1591,6 +1634,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   h->force_shard = getenv("HS_FORCE_SHARD") != nullptr;
   h->shard_use_nccl = getenv("HS_SHARD_NCCL") != nullptr;
   h->hostprof = getenv("HS_HOSTPROF") != nullptr;
+  h->windows = getenv("HS_NO_WINDOW") == nullptr;
   if (const char* pc = getenv("HS_PIPE_CHUNK")) { if (atoi(pc) > 0) h->pipe_chunk = (uint32_t)atoi(pc); }
   if (getenv("HS_TIMING") && h->b_timing.ensure(16)) { h->timing = true; cudaMemset(h->b_timing.d, 0, 16 * sizeof(unsigned long long)); }
   const char* fc = getenv("HS_FAIL_CAP");
@@ -1612,6 +1656,8 @@ void hs_destroy(hs_handle* h) {
   cudaSetDevice(h->device);
   if (h->d_dyn) { cudaFree(h->d_dyn); cudaFree(h->d_stat); cudaFree(h->d_flags); cudaFree(h->d_pair); }
   if (h->d_tot) cudaFree(h->d_tot);
+  if (h->w_skey) { cudaFree(h->w_skey); cudaFree(h->w_rmask); cudaFree(h->w_head); cudaFree(h->w_rank); }
+  if (h->w_stats) cudaFree(h->w_stats);
   h->b_pods.release(); h->b_entries.release(); h->b_uuid.release(); h->b_rel.release(); h->b_dec.release();
   h->b_alloc.release(); h->b_delta.release(); h->b_best.release(); h->b_fail.release(); h->b_counters.release();
   h->b_candpos.release(); h->b_timing.release(); h->b_quota.release();
@@ -2192,12 +2238,24 @@ extern "C" long long hs_launch_divcheck(unsigned long long n, unsigned long long
 long long hs_debug_divcheck(unsigned long long n, unsigned long long seed) { return hs_launch_divcheck(n, seed); }
 
 /* Diagnostic (HS_TIMING=1): cumulative SM clocks block 0 spent per phase of the decide loop:
- * 0 stage, 1 release ops, 2 sweep, 3 reduce, 4 barrier, 5 winner read, 6 commit/explain. */
+ * 0 stage, 1 release ops, 2 sweep, 3 reduce, 4 barrier, 5 winner read, 6 commit/explain, 7 whole windows;
+ * inside the windows (resolver CTA): 8 op staging + sweep, 9 waiting for the arrivals, 10 pre-tracking, 11 the ops in order. */
 int32_t hs_debug_timing(hs_handle* h, unsigned long long out[8]) {
   if (!h || !h->timing) return HS_ERR_INVALID;
   cudaSetDevice(h->device);
   if (cudaMemcpy(h->b_timing.h, h->b_timing.d, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) return HS_ERR_CUDA;
   for (int i = 0; i < 8; i++) out[i] = h->b_timing.h[i];
+  return HS_OK;
+}
+/* … all 16 phase clocks, and the window counters: [0] windows, [1] ops decided in windows, [2] stops on a no-fit op,
+ * [3] stops on a full tracker, [4] winners that had to be loaded in the middle of a window. */
+int32_t hs_debug_window_stats(hs_handle* h, unsigned long long timing16[16], uint32_t stats8[8]) {
+  if (!h) return HS_ERR_INVALID;
+  cudaSetDevice(h->device);
+  for (int i = 0; i < 16; i++) if (timing16) timing16[i] = 0;
+  for (int i = 0; i < 8; i++) if (stats8) stats8[i] = 0;
+  if (timing16 && h->timing && cudaMemcpy(timing16, h->b_timing.d, 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) return HS_ERR_CUDA;
+  if (stats8 && h->w_stats && cudaMemcpy(stats8, h->w_stats, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost) != cudaSuccess) return HS_ERR_CUDA;
   return HS_OK;
 }
 

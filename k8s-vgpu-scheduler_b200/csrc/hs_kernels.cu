@@ -23,6 +23,7 @@
 
 #include "hs_eval.cuh"
 #include "hs_fast.cuh"
+#include "hs_window.cuh"
 
 // Inventory layout (node-major structure-of-arrays): dyn[node*8 + slot] = {used, usedmem, usedcores,
 // dflags}, stat[node*8 + slot] = {count, totalmem, totalcore, packed}.  The 8 lanes of a node read
@@ -271,6 +272,7 @@ hs_decide_kernel(const KernelArgs ka) {
   __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
   __shared__ unsigned long long s_red[32];
   __shared__ unsigned long long s_win;
+  __shared__ WinShared s_ws;
 
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
@@ -300,6 +302,8 @@ hs_decide_kernel(const KernelArgs ka) {
   uint32_t fail_count = 0;     // no-fit decisions so far: identical in every thread
   uint32_t barriers = 0;       // arg-best exchanges so far in this launch: identical in every thread (and rank)
   int r = ka.op_begin;
+  int ring_base = r;           // op whose record sits in s_op[0]: the prefetch ring restarts after every window
+  int no_window_at = -1;       // op that a window left to the one-op path (it found no node: FailedNodes reasons)
   for (int i = 0; i < HS_PF - 1; i++) prefetch_op(ka.pods + r + i, &s_op[i], r + i < ka.n_ops);
 
   const bool timing = ka.timing != nullptr && gtid == 0;   // diagnostic phase clocks (HS_TIMING=1), block 0 only
@@ -307,18 +311,49 @@ hs_decide_kernel(const KernelArgs ka) {
 #define TICK(slot) do { if (timing) { const long long t_ = clock64(); ka.timing[slot] += (unsigned long long)(t_ - tc); tc = t_; } } while (0)
 
   for (; r < ka.n_ops; r++) {
-    const int buf = (r - ka.op_begin) & (HS_PF - 1);
+    const int buf = (r - ring_base) & (HS_PF - 1);
     prefetch_wait_oldest();
     __syncthreads();             // op r is staged; every thread is done with op r-1's buffer and with s_ent
     prefetch_op(ka.pods + r + HS_PF - 1, &s_op[(buf + HS_PF - 1) & (HS_PF - 1)], r + HS_PF - 1 < ka.n_ops);
     const DevPod& pod = s_op[buf];
-    if (resident && __any_sync(FULL, dirty || reload)) {   // warp-uniform: refresh what a commit/release changed
-      if (reload && gg < ka.n_nodes) load_dev(ka, gg, glane, D);
+    // a window works on HBM only: the stale register copies it leaves behind are re-read when a one-op decision needs them
+    const bool will_window = ka.w_skey != nullptr && pod.win_len >= 2 && r != no_window_at;
+    const bool do_reload = reload && !will_window;
+    if (resident && __any_sync(FULL, dirty || do_reload)) {   // warp-uniform: refresh what a commit/release changed
+      if (do_reload && gg < ka.n_nodes) load_dev(ka, gg, glane, D);
       my_pre = fast_node_score(D);
-      if ((dirty || reload) && glane == 0 && gg < ka.n_nodes) ka.node_tot[gg].y = __float_as_int(my_pre);
-      dirty = false; reload = false;
+      if ((dirty || do_reload) && glane == 0 && gg < ka.n_nodes) ka.node_tot[gg].y = __float_as_int(my_pre);
+      dirty = false;
+      if (do_reload) reload = false;
     }
     TICK(0);
+
+    if (will_window) {
+      // ---- a window: this op and the next win_len-1 decided with one sweep and one barrier (hs_window.cuh)
+      int why = 0;
+      const int wlen = min(min((int)pod.win_len, HS_WIN), ka.n_ops - r);
+      const int n_exec = run_window(ka, r, wlen, s_ws, &why);
+      if (why == 1) no_window_at = r + n_exec;
+      if (n_exec > 0) {
+        reload = resident;       // the window committed through HBM: the register copies are stale
+        dirty = false;
+        prefetch_wait();
+        __syncthreads();
+        r += n_exec;
+        ring_base = r;
+        for (int i = 0; i < HS_PF - 1; i++) prefetch_op(ka.pods + r + i, &s_op[i], r + i < ka.n_ops);
+        r--;                     // the loop's own increment
+        TICK(7);
+        continue;
+      }
+      // the window's first op found no node: nothing was changed, the one-op path below writes the reasons — on
+      // current registers: a reload that an earlier window left pending was skipped above
+      if (resident && __any_sync(FULL, reload)) {     // warp-uniform: fast_node_score is a collective
+        if (reload && gg < ka.n_nodes) load_dev(ka, gg, glane, D);
+        my_pre = fast_node_score(D);
+        reload = false;
+      }
+    }
 
     if (pod.op == OP_RELEASE) {
       // podManager.DelPod + usage release (scheduler.go:226-253): the owner subtracts what the commit added.
@@ -624,10 +659,9 @@ hs_decide_kernel(const KernelArgs ka) {
     TICK(6);
   }
   prefetch_wait();
-  if (resident && __any_sync(FULL, dirty || reload)) {   // publish the score of nodes changed by the last ops
-    if (reload && gg < ka.n_nodes) load_dev(ka, gg, glane, D);
-    my_pre = fast_node_score(D);
-    if ((dirty || reload) && glane == 0 && gg < ka.n_nodes) ka.node_tot[gg].y = __float_as_int(my_pre);
+  if (resident && __any_sync(FULL, dirty)) {   // publish the score of nodes changed by the last one-op commits (a pending
+    my_pre = fast_node_score(D);               // reload means HBM is already current: windows and the general path store it)
+    if (dirty && glane == 0 && gg < ka.n_nodes) ka.node_tot[gg].y = __float_as_int(my_pre);
   }
   if (gtid == 0) { ka.counters[2] = (uint32_t)r; ka.counters[1] = fail_count; ka.counters[5] = barriers; }
 }

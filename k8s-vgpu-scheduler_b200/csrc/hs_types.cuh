@@ -10,6 +10,9 @@
 #define HS_MAX_C 16       // containers per pod
 #define HS_MAX_ALLOC 64   // allocation rows one decision can produce
 #define HS_SCORE_SLOTS 4  // distinct Ascend910* type keys per pod that contribute ScoreNode
+#define HS_WIN 16         // ops decided per window: one inventory sweep and one grid barrier serve all of them (hs_window.cuh)
+#define HS_WSLOTS 32      // nodes the window's resolver can track (one quarter warp each: the decide kernel's CTA is 256 threads)
+#define HS_WMAX_TILES 4096 // inventories up to 131,072 nodes per GPU are decided in windows
 
 // ---- inventory in HBM -------------------------------------------------------
 // Structure-of-arrays in tiles of 32 nodes: for tile t, device slot d, lane n
@@ -95,7 +98,8 @@ struct DevPod {             // one op of the stream, 96 B + entries
   float w_slot, w_core, w_mem;   // float32(int64 weight)
   uint32_t entry_off;       // first DevEntry in the entry pool
   uint8_t ctr_begin[HS_MAX_C + 1]; // container c owns entries [ctr_begin[c], ctr_begin[c+1])
-  uint8_t pad3[3];
+  uint8_t win_len;          // ops from this one on that may be decided as ONE window (hs_window.cuh); < 2 = decide it alone
+  uint8_t pad3[2];
   // OP_RELEASE: subtract a committed allocation.
   int32_t rel_node;         // node slot, or -1 = take node and deltas from decision `rel_ref` of this batch
   int32_t rel_ref;
@@ -201,4 +205,11 @@ struct KernelArgs {
   long long* quota;
   OpSync* sync2;                // [op]
   unsigned long long* timing;   // diagnostic: 8 phase-clock accumulators written by block 0 (NULL = off)
+  // windows (hs_window.cuh): per 32-node tile the nodes' arg-best keys sorted best first, per op of the window the fit
+  // bits in that order and the tile's best fitting key; NULL = windows off
+  unsigned long long* w_skey;   // [tile][32]
+  uint32_t* w_rmask;            // [tile][HS_WIN]
+  unsigned long long* w_head;   // [HS_WIN][n_tiles]
+  uint8_t* w_rank;              // [node] rank of the node inside its tile's sorted order
+  uint32_t* w_stats;            // [0] windows, [1] ops decided in windows, [2] stops on no-fit, [3] stops on a full tracker, [4] winners loaded late
 };

@@ -38,6 +38,15 @@ print("ops %d filters %d fits %d nofits %d device_ms %.3f  -> %.2f us/op, %.2f u
       (len(part), nfilt, nf, nn, ms, 1e3 * ms / len(part), 1e3 * ms / nfilt))
 for nm, v in zip(names, d):
     print("  %-15s %12d clk  %5.1f%%  %.2f us/decision @1.965GHz" % (nm, v, 100.0 * v / tot, v / 1965.0 / nfilt))
+# windows (hs_window.cuh): the resolver's clocks and the window counters
+L.hs_debug_window_stats.argtypes = [C.c_void_p, C.POINTER(C.c_ulonglong), C.POINTER(C.c_uint32)]
+t16, st = (C.c_ulonglong * 16)(), (C.c_uint32 * 8)()
+L.hs_debug_window_stats(e.h, t16, st)
+if st[0]:
+    print("windows %d (both batches), ops decided in windows %d (%.1f per window), stops: no-fit %d, tracker full %d; winners loaded late %d"
+          % (st[0], st[1], st[1] / st[0], st[2], st[3], st[4]))
+    for nm, i in (("whole windows (any CTA 0 view)", 7), ("stage+sweep", 8), ("wait arrivals", 9), ("pre-track", 10), ("ops in order", 11)):
+        print("  %-32s %12d clk  %.2f us/window @1.965GHz" % (nm, t16[i], t16[i] / 1965.0 / st[0]))
 L.hs_debug_host_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
 hs = (C.c_double * 4)()
 L.hs_debug_host_seconds(e.h, hs)
