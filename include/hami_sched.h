@@ -315,6 +315,17 @@ int32_t hs_filter(hs_handle* h, const hs_pod* pod,
  * so assignments equal n sequential hs_filter/hs_pod_delete calls.
  * Candidates are every registered node.  Returns the number of ops run.     */
 int32_t hs_run_batch(hs_handle* h, const hs_op* ops, uint32_t n_ops);
+/* The same, without waiting for the end of the batch: a long batch runs as a pipeline inside the library (request
+ * compile of chunk c+1 | device run of chunk c | usage-cache update of chunk c-1) and the call returns as soon as
+ * that pipeline is started, so the caller can read the results of the first chunks (hs_batch_get, hs_batch_summary;
+ * both wait for the op they read) while the device still decides the later ones.  `ops` and everything it points to
+ * must stay valid until the batch has finished: hs_batch_wait(h, HS_BATCH_ALL), a complete hs_batch_summary, or any
+ * other call on the handle (each of them first lets the pipeline finish).  No callback enters the caller's code and no
+ * caller pointer is kept beyond the batch (cgo rules).  Short batches simply run to completion inside the call.     */
+int32_t hs_run_batch_async(hs_handle* h, const hs_op* ops, uint32_t n_ops);
+#define HS_BATCH_ALL 0xffffffffu
+/* Blocks until result i of the running batch can be read; HS_BATCH_ALL: until the whole batch has finished. */
+int32_t hs_batch_wait(hs_handle* h, uint32_t i);
 /* Result i of the last hs_run_batch (DELETE ops yield status HS_OK, no node). */
 int32_t hs_batch_get(hs_handle* h, uint32_t i, hs_filter_result* out);
 

@@ -15,7 +15,11 @@
 #include <cstring>
 #include <deque>
 #include <future>
+#include <condition_variable>
 #include <map>
+#include <memory>
+#include <mutex>
+#include <thread>
 #include <set>
 #include <string>
 #include <unordered_map>
@@ -35,6 +39,7 @@ extern "C" int hs_launch_shard_explain(const KernelArgs* ka, int op, int grid, c
 
 namespace {
 
+struct BatchJob;
 std::string g_create_error;
 
 // ---- Go string helpers (ASCII subset, as the reference's inputs are) ------------------------
@@ -249,7 +254,7 @@ struct hs_handle {
   unsigned long long* w_skey = nullptr; uint32_t* w_rmask = nullptr; unsigned long long* w_head = nullptr; uint8_t* w_rank = nullptr;
   uint32_t* w_stats = nullptr;
   int w_cap_nodes = 0;
-  bool windows = true;                 // HS_NO_WINDOW=1: every op takes the one-op path (A/B runs, tests)
+  bool windows = false;                // HS_WINDOW=1: decide runs of common-shape ops in windows (hs_window.cuh); measured slower than the one-op path on C3, so off by default
   DBuf<unsigned long long> b_timing;   // HS_TIMING=1: phase clocks of block 0
   bool timing = false;
   // sharded mode (one process per GPU): contiguous node block per rank, NCCL allreduce-max of the packed key per decision
@@ -289,13 +294,14 @@ struct hs_handle {
   hs_handle* sim = nullptr;             // child handle holding the transient inventory of hs_filter_simulate
   bool dry_run = false;                 // set around hs_filter_dry: ops neither release nor commit
   uint64_t bytes_h2d = 0, bytes_d2h = 0;  // measured host<->device copy volume of the batch path
+  std::unique_ptr<BatchJob> job;  // the batch of the last hs_run_batch (compile state + pipeline)
   size_t n_parked = 0;                  // PodRec::parked entries alive in h->pods
   bool poisoned = false;                // a CUDA call failed while a batch was on the device: HBM and the host mirror may differ
   bool hostprof = false;                // HS_HOSTPROF=1: split the summary time by result kind, printed at hs_destroy
   double prof_s[4] = {0, 0, 0, 0};      // fit / no-fit / other / count
   double host_s[4] = {0, 0, 0, 0};      // diagnostic: cumulative host seconds in compile / device+copies / absorb / summary
   uint32_t fail_cap = 32;
-  uint32_t pipe_chunk = 2048;
+  uint32_t pipe_chunk = 512;
   int sync2_base = 0;                   // first quota-barrier slot in b_best (== op capacity of the current batch)
   int grid_now = 1;                     // grid of the decide kernel for the current batch
   uint32_t fail_cap_now = 32;           // no-fit decisions one launch can hold before the host drains the reasons
@@ -306,8 +312,8 @@ struct hs_handle {
   std::vector<std::string> cand_names;  // explicit candidate list of the last hs_filter
   std::vector<int> cand_slot;
   bool have_cand = false;
-  std::vector<DevFail> fail_host;       // drained fail records: [slot][cap_nodes]
-  std::vector<uint32_t> op_fail_slot;   // per device op: slot in fail_host or ~0
+  std::deque<std::vector<DevFail>> fail_segs;   // drained fail records, one segment per drain: [slot][n_nodes] (segments never move)
+  std::vector<const DevFail*> op_fail_row;      // per device op: its [n_nodes] reason records, or NULL
 
   // mask cache
   std::unordered_map<std::string, std::array<uint64_t, 4>> mask_cache;
@@ -865,8 +871,8 @@ int device_begin(hs_handle* h, int max_ops, uint32_t alloc_bound) {
   const int maxb = hs_decide_max_blocks(block, h->device);
   if (maxb <= 0) { h->err = "hs_decide_kernel cannot be launched cooperatively on this device"; return HS_ERR_CUDA; }
   h->grid_now = std::min(std::min(maxb, 1024), std::max(1, (n_nodes * HS_D + block - 1) / block));   // 8 lanes per node when it fits
-  h->fail_host.clear();
-  h->op_fail_slot.assign(max_ops, 0xffffffffu);
+  h->fail_segs.clear();
+  h->op_fail_row.assign(max_ops, nullptr);
   h->last_ms = 0;
   return HS_OK;
 }
@@ -901,20 +907,19 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
     uint32_t ran = h->b_counters.h[2] - (uint32_t)done, nfail = h->b_counters.h[1];
     h->epoch_base += h->b_counters.h[5];
     if (h->b_counters.h[6]) { h->err = "fused multi-GPU arg-best: a peer rank never arrived (ranks must submit the same ops)"; return HS_ERR_CUDA; }
+    const DevFail* seg = nullptr;
     if (nfail) {
-      size_t base = h->fail_host.size();
-      h->fail_host.resize(base + (size_t)nfail * n_nodes);
       CUDA_OK(h, down(h, h->b_fail.h, h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail)));
       CUDA_OK(h, cudaStreamSynchronize(h->stream));
-      memcpy(h->fail_host.data() + base, h->b_fail.h, (size_t)nfail * n_nodes * sizeof(DevFail));
+      h->fail_segs.emplace_back(h->b_fail.h, h->b_fail.h + (size_t)nfail * n_nodes);
+      seg = h->fail_segs.back().data();
     }
     if (ran == 0 && nfail == 0 && n_ops - done > 0) { h->err = "decide kernel made no progress"; return HS_ERR_CUDA; }
     // decisions of this launch
     CUDA_OK(h, down_sync(h, h->b_dec.h + done, h->b_dec.d + done, (size_t)ran * sizeof(DevDecision)));
-    uint32_t slot_base = (uint32_t)(h->fail_host.size() / std::max(n_nodes, 1)) - nfail;
     for (uint32_t i = 0; i < ran; i++) {
       DevDecision& d = h->b_dec.h[done + i];
-      if (d.status == 1 && d.fail_slot != 0xffffffffu) h->op_fail_slot[done + i] = slot_base + d.fail_slot;
+      if (d.status == 1 && d.fail_slot < nfail) h->op_fail_row[done + i] = seg + (size_t)d.fail_slot * n_nodes;
     }
     done += (int)ran;
     if (done < n_ops) {
@@ -1019,15 +1024,15 @@ int run_device_ops_sharded(hs_handle* h, int n_ops, size_t n_entries, size_t n_u
   const uint32_t nalloc = std::min(h->b_counters.h[0], alloc_cap);
   if (nalloc) CUDA_OK(h, down_sync(h, h->b_alloc.h, h->b_alloc.d, (size_t)nalloc * sizeof(DevAlloc)));
   const uint32_t nfail = std::min(h->b_counters.h[1], shard_fail_cap);
-  h->fail_host.clear();
-  h->op_fail_slot.assign(n_ops, 0xffffffffu);
+  h->fail_segs.clear();
+  h->op_fail_row.assign(n_ops, nullptr);
   if (nfail) {
-    h->fail_host.resize((size_t)nfail * n_nodes);
-    CUDA_OK(h, down_sync(h, h->fail_host.data(), h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail)));
+    h->fail_segs.emplace_back((size_t)nfail * n_nodes);
+    CUDA_OK(h, down_sync(h, h->fail_segs.back().data(), h->b_fail.d, (size_t)nfail * n_nodes * sizeof(DevFail)));
   }
   for (int op = 0; op < n_ops; op++) {
     const DevDecision& d = h->b_dec.h[op];
-    if (d.status == 1 && d.fail_slot < nfail) h->op_fail_slot[op] = d.fail_slot;
+    if (d.status == 1 && d.fail_slot < nfail) h->op_fail_row[op] = h->fail_segs.back().data() + (size_t)d.fail_slot * n_nodes;
   }
   return HS_OK;
 }
@@ -1229,12 +1234,10 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
     out->score = dec.score;
   } else if (dec.status == 1) {
     out->status = HS_NOFIT;
-    uint32_t slot = h->op_fail_slot[op];
-    const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
+    const DevFail* fr = h->op_fail_row[op];
     auto reason_of = [&](int node) -> const char* {
-      if (slot == 0xffffffffu) return "";
-      const DevFail& f = h->fail_host[(size_t)slot * n_nodes + node];
-      return fail_string(h, f).c_str();
+      if (!fr) return "";
+      return fail_string(h, fr[node]).c_str();
     };
     if (h->have_cand) {
       for (size_t i = 0; i < h->cand_names.size(); i++) {
@@ -1248,10 +1251,9 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
       const size_t nn = h->nodes.size();
       h->r_failed.resize(nn);
       size_t k = 0;
-      if (slot == 0xffffffffu) {
+      if (!fr) {
         for (size_t s = 0; s < nn; s++) if (h->h_flags[s] & NF_ALIVE) h->r_failed[k++] = hs_failed_node{h->name_ptr[s], ""};
       } else {
-        const DevFail* fr = h->fail_host.data() + (size_t)slot * n_nodes;
         const char* last = nullptr;
         uint32_t l0 = 0xffffffffu, l1 = 0, l2 = 0;
         for (size_t s = 0; s < nn; s++) {
@@ -1335,8 +1337,8 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
 }
 
 // Apply the finished batch to the host mirrors: usage cache + podManager.
-void absorb_results(hs_handle* h, int n_ops) {
-  for (int op = 0; op < n_ops; op++) {
+void absorb_results(hs_handle* h, int first, int last) {
+  for (int op = first; op < last; op++) {
     const OpMeta& m = h->metas[op];
     const DevDecision& dec = h->b_dec.h[op];
     if (m.kind == OP_FILTER && m.status == HS_OK && dec.status == 0 && !m.dry) {
@@ -1402,81 +1404,232 @@ int poison(hs_handle* h, int rc) {
   return rc;
 }
 
-int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
-  if (h->poisoned) { h->err = "handle is unusable after an earlier device failure (hs_destroy and rebuild it)"; return HS_ERR_CUDA; }
-  const double t0 = now_s();
+// One hs_run_batch in flight: the compile state (what the ops have been turned into so far) and, for long batches, the
+// three-stage pipeline  compile thread -> device thread -> caller  (hs_batch_wait / hs_batch_get / hs_batch_summary):
+// while the device runs chunk c the compile thread prepares chunk c+1 and absorbs the results of chunk c-1 into the
+// host mirrors, and the caller can already materialise the results of every finished chunk.
+struct BatchJob {
+  const hs_op* ops = nullptr;
+  uint32_t n_ops = 0;
   std::vector<DevPod> pods;
   std::vector<DevEntry> entries;
   std::vector<uint32_t> uuid_pool;
   std::vector<int4> rel;
   std::unordered_map<std::string, int> in_batch;
   std::unordered_set<std::string> released;   // known pods with a release staged in this batch (h->pods is untouched until absorb)
+  uint32_t alloc_cap = 0;
+  StageMark staged;
+  Compiled c;
+  // pipeline
+  struct Chunk { int first = 0, last = 0; StageMark from, to; uint32_t alloc_from = 0, alloc_to = 0; };
+  std::vector<Chunk> chunks;
+  uint32_t chunk_ops = 0;
+  int n_staged = 0, n_done = 0, n_absorbed = 0;
+  bool compile_finished = false, active = false;
+  int rc = HS_OK;
+  uint32_t alloc_bound = 0;
+  int max_ops = 0;
+  double t_begin = 0, t_first_submit = 0, t_device_done = 0;
+  std::thread t_compile, t_device;
+  std::mutex mu;
+  std::condition_variable cv;
+};
+
+void job_compile_range(hs_handle* h, BatchJob& j, uint32_t i0, uint32_t i1) {
+  for (uint32_t i = i0; i < i1; i++) {
+    const hs_pod* pod = j.ops[i].pod;
+    if (!pod || !pod->uid) { h->user_status[i] = HS_ERR_INVALID; continue; }
+    std::string uid = pod->uid;
+    if (j.ops[i].kind == HS_OP_DELETE) {
+      if (stage_release(h, uid, j.in_batch, j.released, j.pods, j.rel, h->metas, (int)i)) h->user_first_op[i] = (int)j.pods.size() - 1;
+      else h->user_status[i] = HS_ERR_NOTFOUND;
+      continue;
+    }
+    int rc = compile_pod(h, pod, j.uuid_pool, j.c);
+    if (rc != HS_OK) { h->user_status[i] = rc; continue; }
+    if (h->dry_run) { j.c.pod.flags |= PF_DRYRUN; j.c.meta.dry = true; }   // simulation runs before TakeAndDeletePod (scheduler.go:1088-1094)
+    else stage_release(h, uid, j.in_batch, j.released, j.pods, j.rel, h->metas, -1);  // TakeAndDeletePod
+    j.c.pod.entry_off = (uint32_t)j.entries.size();
+    j.entries.insert(j.entries.end(), j.c.entries.begin(), j.c.entries.end());
+    j.c.meta.user_op = (int)i;
+    j.c.pod.alloc_base = j.alloc_cap;
+    j.pods.push_back(j.c.pod);
+    h->metas.push_back(j.c.meta);
+    if (!h->dry_run) j.in_batch[uid] = (int)j.pods.size() - 1;
+    h->user_first_op[i] = (int)j.pods.size() - 1;
+    j.alloc_cap += j.c.max_alloc;
+  }
+}
+
+// Copy what the last compile appended into the pinned staging buffers.  A buffer that has to grow is reallocated and then
+// holds everything again — the device must be idle for that (`wait_idle` is called first when a pipeline is running).
+template <class WaitIdle>
+int job_stage(hs_handle* h, BatchJob& j, StageMark& mark, WaitIdle wait_idle) {
+  const bool grow = j.pods.size() > h->b_pods.cap || j.entries.size() > h->b_entries.cap || j.uuid_pool.size() > h->b_uuid.cap ||
+                    j.rel.size() > h->b_rel.cap;
+  if (grow) wait_idle();
+  const size_t cp = h->b_pods.cap, ce = h->b_entries.cap, cu = h->b_uuid.cap, cr = h->b_rel.cap;
+  if (!h->b_pods.ensure(std::max<size_t>(j.pods.size(), 1)) || !h->b_entries.ensure(std::max<size_t>(j.entries.size(), 1)) ||
+      !h->b_uuid.ensure(std::max<size_t>(j.uuid_pool.size(), 1)) || !h->b_rel.ensure(std::max<size_t>(j.rel.size(), 1))) {
+    h->err = "out of memory for batch staging";
+    return HS_ERR_CUDA;
+  }
+  StageMark& staged = j.staged;
+  if (h->b_pods.cap != cp) { staged.pods = 0; mark.pods = 0; }
+  if (h->b_entries.cap != ce) { staged.entries = 0; mark.entries = 0; }
+  if (h->b_uuid.cap != cu) { staged.uuid = 0; mark.uuid = 0; }
+  if (h->b_rel.cap != cr) { staged.rel = 0; mark.rel = 0; }
+  mark_windows(j.pods, staged.pods);
+  memcpy(h->b_pods.h + staged.pods, j.pods.data() + staged.pods, (j.pods.size() - staged.pods) * sizeof(DevPod));
+  if (j.entries.size() > staged.entries) memcpy(h->b_entries.h + staged.entries, j.entries.data() + staged.entries, (j.entries.size() - staged.entries) * sizeof(DevEntry));
+  if (j.uuid_pool.size() > staged.uuid) memcpy(h->b_uuid.h + staged.uuid, j.uuid_pool.data() + staged.uuid, (j.uuid_pool.size() - staged.uuid) * sizeof(uint32_t));
+  if (j.rel.size() > staged.rel) memcpy(h->b_rel.h + staged.rel, j.rel.data() + staged.rel, (j.rel.size() - staged.rel) * sizeof(int4));
+  staged.pods = j.pods.size(); staged.entries = j.entries.size(); staged.uuid = j.uuid_pool.size(); staged.rel = j.rel.size();
+  return HS_OK;
+}
+
+// ---- the pipeline's two threads -------------------------------------------------------------------------------
+void job_device_loop(hs_handle* h, BatchJob* jp) {
+  BatchJob& j = *jp;
+  cudaSetDevice(h->device);
+  for (int k = 0;; k++) {
+    BatchJob::Chunk ch;
+    {
+      std::unique_lock<std::mutex> lk(j.mu);
+      j.cv.wait(lk, [&] { return j.n_staged > k || j.compile_finished || j.rc != HS_OK; });
+      if (j.rc != HS_OK || j.n_staged <= k) break;
+      ch = j.chunks[k];
+    }
+    if (k == 0) j.t_first_submit = now_s();
+    int rc = HS_OK;
+    if (ch.last > ch.first) {
+      rc = device_range(h, ch.first, ch.last, ch.from, ch.to, j.alloc_bound);
+      // this chunk's allocation rows and collapsed deltas come back with it: absorb and result assembly need nothing else
+      if (rc == HS_OK && ch.alloc_to > ch.alloc_from &&
+          down_sync(h, h->b_alloc.h + ch.alloc_from, h->b_alloc.d + ch.alloc_from, (size_t)(ch.alloc_to - ch.alloc_from) * sizeof(DevAlloc)) != cudaSuccess) rc = HS_ERR_CUDA;
+      if (rc == HS_OK && down_sync(h, h->b_delta.h + (size_t)ch.first * HS_D, h->b_delta.d + (size_t)ch.first * HS_D,
+                                   (size_t)(ch.last - ch.first) * HS_D * sizeof(int4)) != cudaSuccess) rc = HS_ERR_CUDA;
+      if (rc == HS_ERR_CUDA && h->err.empty()) h->err = "copying a chunk's results back failed";
+    }
+    {
+      std::lock_guard<std::mutex> lk(j.mu);
+      if (rc != HS_OK) j.rc = rc; else j.n_done = k + 1;
+    }
+    j.cv.notify_all();
+    if (rc != HS_OK) break;
+  }
+  j.t_device_done = now_s();
+}
+
+void absorb_results(hs_handle* h, int first, int last);
+
+void job_compile_loop(hs_handle* h, BatchJob* jp) {
+  BatchJob& j = *jp;
+  cudaSetDevice(h->device);
+  auto absorb_ready = [&](bool block) {
+    for (;;) {
+      int k = -1;
+      {
+        std::unique_lock<std::mutex> lk(j.mu);
+        if (block) j.cv.wait(lk, [&] { return j.n_done > j.n_absorbed || j.rc != HS_OK || j.n_absorbed >= j.n_staged; });
+        if (j.rc == HS_OK && j.n_done > j.n_absorbed) k = j.n_absorbed;
+      }
+      if (k < 0) return;
+      absorb_results(h, j.chunks[k].first, j.chunks[k].last);
+      std::lock_guard<std::mutex> lk(j.mu);
+      j.n_absorbed = k + 1;
+    }
+  };
+  auto wait_idle = [&] {       // the device has run everything staged so far
+    std::unique_lock<std::mutex> lk(j.mu);
+    j.cv.wait(lk, [&] { return j.n_done >= j.n_staged || j.rc != HS_OK; });
+  };
+  StageMark uploaded;
+  int first = 0;
+  for (uint32_t i0 = 0; i0 < j.n_ops; i0 += j.chunk_ops) {
+    const uint32_t i1 = std::min<uint32_t>(j.n_ops, i0 + j.chunk_ops);
+    const uint32_t alloc_from = j.alloc_cap;
+    job_compile_range(h, j, i0, i1);
+    int rc = job_stage(h, j, uploaded, wait_idle);
+    BatchJob::Chunk ch;
+    ch.first = first; ch.last = (int)j.pods.size(); ch.from = uploaded; ch.to = j.staged;
+    ch.alloc_from = alloc_from; ch.alloc_to = j.alloc_cap;
+    {
+      std::lock_guard<std::mutex> lk(j.mu);
+      if (rc != HS_OK) j.rc = rc;
+      else { j.chunks.push_back(ch); j.n_staged++; }
+    }
+    j.cv.notify_all();
+    if (rc != HS_OK) return;
+    uploaded = j.staged;
+    first = ch.last;
+    absorb_ready(false);                        // whatever the device has finished in the meantime
+    { std::lock_guard<std::mutex> lk(j.mu); if (j.rc != HS_OK) return; }
+  }
+  { std::lock_guard<std::mutex> lk(j.mu); j.compile_finished = true; }
+  j.cv.notify_all();
+  for (;;) {                                    // drain: absorb the remaining chunks as they finish
+    absorb_ready(true);
+    std::lock_guard<std::mutex> lk(j.mu);
+    if (j.rc != HS_OK || j.n_absorbed >= j.n_staged) return;
+  }
+}
+
+// Wait for the pipeline of the current batch (if any) to finish, fold its outcome into the handle.
+int job_finish(hs_handle* h) {
+  BatchJob* jp = h->job.get();
+  if (!jp || !jp->active) return HS_OK;
+  BatchJob& j = *jp;
+  if (j.t_compile.joinable()) j.t_compile.join();
+  if (j.t_device.joinable()) j.t_device.join();
+  j.active = false;
+  const double t_end = now_s();
+  if (j.rc != HS_OK) return poison(h, j.rc);
+  // exposed host time: before the first chunk reached the device, and after the device finished
+  h->host_s[0] += std::max(0.0, j.t_first_submit - j.t_begin);
+  h->host_s[1] += std::max(0.0, j.t_device_done - j.t_first_submit);
+  h->host_s[2] += std::max(0.0, t_end - j.t_device_done);
+  return HS_OK;
+}
+
+// Block until the result of caller op `i` of the current batch can be read (its chunk has left the device).
+int job_wait_user(hs_handle* h, uint32_t i) {
+  BatchJob* jp = h->job.get();
+  if (!jp || !jp->active) return HS_OK;
+  BatchJob& j = *jp;
+  const int k = (int)(i / j.chunk_ops);
+  std::unique_lock<std::mutex> lk(j.mu);
+  j.cv.wait(lk, [&] { return j.n_done > k || j.rc != HS_OK; });
+  return j.rc;
+}
+
+// Compile caller ops into device ops (implicit release of a pod that is filtered again, scheduler.go:1092-1094), run
+// them, absorb the results.  `async`: a long batch returns as soon as its pipeline is running.
+int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops, bool async = false) {
+  int frc = job_finish(h);
+  if (frc != HS_OK) return frc;
+  if (h->poisoned) { h->err = "handle is unusable after an earlier device failure (hs_destroy and rebuild it)"; return HS_ERR_CUDA; }
+  const double t0 = now_s();
+  h->job.reset(new BatchJob());
+  BatchJob& j = *h->job;
+  j.ops = ops; j.n_ops = n_ops;
   h->metas.clear();
   h->user_first_op.assign(n_ops, -1);
   h->user_status.assign(n_ops, HS_OK);
   h->quota_rows.clear();
-  uint32_t alloc_cap = 0;
-  Compiled c;
-  auto compile_range = [&](uint32_t i0, uint32_t i1) {
-    for (uint32_t i = i0; i < i1; i++) {
-      const hs_pod* pod = ops[i].pod;
-      if (!pod || !pod->uid) { h->user_status[i] = HS_ERR_INVALID; continue; }
-      std::string uid = pod->uid;
-      if (ops[i].kind == HS_OP_DELETE) {
-        if (stage_release(h, uid, in_batch, released, pods, rel, h->metas, (int)i)) h->user_first_op[i] = (int)pods.size() - 1;
-        else h->user_status[i] = HS_ERR_NOTFOUND;
-        continue;
-      }
-      int rc = compile_pod(h, pod, uuid_pool, c);
-      if (rc != HS_OK) { h->user_status[i] = rc; continue; }
-      if (h->dry_run) { c.pod.flags |= PF_DRYRUN; c.meta.dry = true; }   // simulation runs before TakeAndDeletePod (scheduler.go:1088-1094)
-      else stage_release(h, uid, in_batch, released, pods, rel, h->metas, -1);  // TakeAndDeletePod
-      c.pod.entry_off = (uint32_t)entries.size();
-      entries.insert(entries.end(), c.entries.begin(), c.entries.end());
-      c.meta.user_op = (int)i;
-      c.pod.alloc_base = alloc_cap;
-      pods.push_back(c.pod);
-      h->metas.push_back(c.meta);
-      if (!h->dry_run) in_batch[uid] = (int)pods.size() - 1;
-      h->user_first_op[i] = (int)pods.size() - 1;
-      alloc_cap += c.max_alloc;
-    }
-  };
-  // copy what the last compile_range appended into the pinned staging buffers (the device must be idle: a buffer that
-  // has to grow is reallocated and then holds everything again)
-  StageMark staged;
-  auto stage = [&](StageMark& mark) -> int {
-    const size_t cp = h->b_pods.cap, ce = h->b_entries.cap, cu = h->b_uuid.cap, cr = h->b_rel.cap;
-    if (!h->b_pods.ensure(std::max<size_t>(pods.size(), 1)) || !h->b_entries.ensure(std::max<size_t>(entries.size(), 1)) ||
-        !h->b_uuid.ensure(std::max<size_t>(uuid_pool.size(), 1)) || !h->b_rel.ensure(std::max<size_t>(rel.size(), 1))) {
-      h->err = "out of memory for batch staging";
-      return HS_ERR_CUDA;
-    }
-    if (h->b_pods.cap != cp) { staged.pods = 0; mark.pods = 0; }
-    if (h->b_entries.cap != ce) { staged.entries = 0; mark.entries = 0; }
-    if (h->b_uuid.cap != cu) { staged.uuid = 0; mark.uuid = 0; }
-    if (h->b_rel.cap != cr) { staged.rel = 0; mark.rel = 0; }
-    mark_windows(pods, staged.pods);
-    memcpy(h->b_pods.h + staged.pods, pods.data() + staged.pods, (pods.size() - staged.pods) * sizeof(DevPod));
-    if (entries.size() > staged.entries) memcpy(h->b_entries.h + staged.entries, entries.data() + staged.entries, (entries.size() - staged.entries) * sizeof(DevEntry));
-    if (uuid_pool.size() > staged.uuid) memcpy(h->b_uuid.h + staged.uuid, uuid_pool.data() + staged.uuid, (uuid_pool.size() - staged.uuid) * sizeof(uint32_t));
-    if (rel.size() > staged.rel) memcpy(h->b_rel.h + staged.rel, rel.data() + staged.rel, (rel.size() - staged.rel) * sizeof(int4));
-    staged.pods = pods.size(); staged.entries = entries.size(); staged.uuid = uuid_pool.size(); staged.rel = rel.size();
-    return HS_OK;
-  };
 
   const bool launch_per_op = h->force_shard || (h->shard_world > 1 && (!h->xgpu_connected || h->shard_use_nccl));
   // Long batches on the plain single-GPU path are compiled in chunks: while the device runs chunk c, the host compiles
   // chunk c+1 (op indices, in-batch references and the allocation offsets are batch-wide, so the chunks are one stream
   // to the kernel).  Quota rows are gathered by the compile and uploaded once, so quota'd handles take one chunk.
-  const uint32_t kChunk = h->pipe_chunk;   // 2048 user ops; HS_PIPE_CHUNK overrides (tests)
+  const uint32_t kChunk = h->pipe_chunk;   // user ops per chunk; HS_PIPE_CHUNK overrides (tests)
   const bool pipelined = !launch_per_op && h->shard_world <= 1 && !h->have_cand && !h->dry_run && !h->any_quota_limit && n_ops > kChunk;
   if (!pipelined) {
-    compile_range(0, n_ops);
-    int n = (int)pods.size();
+    job_compile_range(h, j, 0, n_ops);
+    int n = (int)j.pods.size();
     if (n == 0) return HS_OK;
     StageMark up;
-    int rc = stage(up);
+    int rc = job_stage(h, j, up, [] {});
     if (rc != HS_OK) return rc;
     if (!h->quota_rows.empty()) {
       if (h->shard_world > 1 || h->force_shard) { h->err = "namespace quotas are not supported on the sharded path"; return HS_ERR_UNSUPPORTED; }
@@ -1491,78 +1644,56 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
       }
     }
     const double t1 = now_s();
-    if (launch_per_op) rc = run_device_ops_sharded(h, n, entries.size(), uuid_pool.size(), rel.size(), alloc_cap);
+    if (launch_per_op) rc = run_device_ops_sharded(h, n, j.entries.size(), j.uuid_pool.size(), j.rel.size(), j.alloc_cap);
     else {
-      rc = device_begin(h, n, alloc_cap);
-      if (rc == HS_OK) rc = device_range(h, 0, n, StageMark(), staged, alloc_cap);
-      if (rc == HS_OK) rc = device_end(h, n, alloc_cap);
+      rc = device_begin(h, n, j.alloc_cap);
+      if (rc == HS_OK) rc = device_range(h, 0, n, StageMark(), j.staged, j.alloc_cap);
+      if (rc == HS_OK) rc = device_end(h, n, j.alloc_cap);
     }
     if (rc != HS_OK) return poison(h, rc);
     const double t2 = now_s();
-    absorb_results(h, n);
+    absorb_results(h, 0, n);
     const double t3 = now_s();
     h->host_s[0] += t1 - t0; h->host_s[1] += t2 - t1; h->host_s[2] += t3 - t2;
     return HS_OK;
   }
 
-  // ---- pipelined: bounds first (device-written buffers must not move while a chunk is in flight)
+  // ---- pipelined: bounds first — nothing the device writes, the caller reads or a thread appends to may move while
+  // the pipeline runs
   uint32_t alloc_bound = 0;
+  size_t entry_bound = 0;
   for (uint32_t i = 0; i < n_ops; i++) {
     const hs_pod* pod = ops[i].pod;
     if (!pod || ops[i].kind == HS_OP_DELETE) continue;
-    for (uint32_t ci = 0; ci < pod->n_containers; ci++)
+    for (uint32_t ci = 0; ci < pod->n_containers; ci++) {
+      entry_bound += pod->containers[ci].n_reqs;
       for (uint32_t r = 0; r < pod->containers[ci].n_reqs; r++) {
         const int32_t nums = pod->containers[ci].reqs[r].nums;
         alloc_bound += (uint32_t)(nums < 0 ? 0 : (nums > HS_D ? HS_D : nums));
       }
+    }
   }
   const int max_ops = (int)(2 * (size_t)n_ops + 1);      // every Filter may carry an implicit release of the pod's earlier decision
-  double compile_s = 0, device_s = 0;
-  double tc0 = now_s();
-  compile_range(0, kChunk);
-  compile_s += now_s() - tc0;
+  h->metas.reserve((size_t)max_ops);
+  j.pods.reserve((size_t)max_ops);
+  if (!h->b_pods.ensure((size_t)max_ops) || !h->b_entries.ensure(std::max<size_t>(entry_bound, 1)) || !h->b_rel.ensure((size_t)max_ops * HS_D)) {
+    h->err = "out of memory for batch staging";
+    return HS_ERR_CUDA;
+  }
   int rc = device_begin(h, max_ops, alloc_bound);
   if (rc != HS_OK) return poison(h, rc);
-  StageMark uploaded;
-  int first = 0;
-  uint32_t next_user = kChunk;
-  while (true) {
-    const double td0 = now_s();
-    rc = stage(uploaded);
-    if (rc != HS_OK) return first > 0 ? poison(h, rc) : rc;   // earlier chunks already ran on the device
-    const int last = (int)pods.size();
-    const StageMark from = uploaded, to = staged;
-    const uint32_t cap_now = alloc_bound;
-    std::future<int> fut;
-    const bool more = next_user < n_ops;
-    if (last > first) fut = std::async(std::launch::async, [h, first, last, from, to, cap_now] { return device_range(h, first, last, from, to, cap_now); });
-    if (more) {                                            // overlapped with the device
-      const double tcc = now_s();
-      const uint32_t i1 = std::min<uint32_t>(n_ops, next_user + kChunk);
-      compile_range(next_user, i1);
-      next_user = i1;
-      compile_s += now_s() - tcc;
-    }
-    if (fut.valid()) { rc = fut.get(); if (rc != HS_OK) return poison(h, rc); }
-    device_s += now_s() - td0;
-    uploaded = to;
-    first = last;
-    if (!more && (int)pods.size() == first) break;
-  }
-  const int n = (int)pods.size();
-  if (n == 0) return HS_OK;
-  const double te0 = now_s();
-  rc = device_end(h, n, alloc_cap);
-  if (rc != HS_OK) return poison(h, rc);
-  device_s += now_s() - te0;
-  const double t2 = now_s();
-  absorb_results(h, n);
-  const double t3 = now_s();
-  // compile time that ran under the device is counted in both columns' wall clock only once: report the exposed part
-  h->host_s[0] += std::max(0.0, (t2 - t0) - device_s); h->host_s[1] += device_s; h->host_s[2] += t3 - t2;
-  (void)compile_s;
-  return HS_OK;
+  j.alloc_bound = alloc_bound; j.max_ops = max_ops; j.chunk_ops = kChunk;
+  j.chunks.reserve((size_t)(n_ops / kChunk + 2));
+  j.t_begin = t0;
+  j.active = true;
+  j.t_device = std::thread(job_device_loop, h, &j);
+  j.t_compile = std::thread(job_compile_loop, h, &j);
+  if (async) return HS_OK;
+  return job_finish(h);
 }
+
+// every entry point but the result readers first lets a running pipeline finish
+#define HS_IDLE(h) do { int _rc = job_finish(h); if (_rc != HS_OK) return _rc; } while (0)
 
 }  // namespace
 
@@ -1634,7 +1765,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   h->force_shard = getenv("HS_FORCE_SHARD") != nullptr;
   h->shard_use_nccl = getenv("HS_SHARD_NCCL") != nullptr;
   h->hostprof = getenv("HS_HOSTPROF") != nullptr;
-  h->windows = getenv("HS_NO_WINDOW") == nullptr;
+  h->windows = getenv("HS_WINDOW") != nullptr;
   if (const char* pc = getenv("HS_PIPE_CHUNK")) { if (atoi(pc) > 0) h->pipe_chunk = (uint32_t)atoi(pc); }
   if (getenv("HS_TIMING") && h->b_timing.ensure(16)) { h->timing = true; cudaMemset(h->b_timing.d, 0, 16 * sizeof(unsigned long long)); }
   const char* fc = getenv("HS_FAIL_CAP");
@@ -1648,6 +1779,7 @@ hs_handle* hs_create(const hs_config* cfg) {
 }
 
 void hs_destroy(hs_handle* h) {
+  if (h) job_finish(h);
   if (h && h->sim) { hs_destroy(h->sim); h->sim = nullptr; }
   if (h && h->hostprof)
     fprintf(stderr, "[hs hostprof] summary: fit %.3f ms, no-fit %.3f ms, other %.3f ms over %.0f results\n", 1e3 * h->prof_s[0],
@@ -1677,6 +1809,7 @@ int32_t hs_node_count(const hs_handle* h) { return h->n_alive; }
 
 int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
   if (!h || !node || !node->name) return HS_ERR_INVALID;
+  HS_IDLE(h);
   if (node->n_devices > HS_MAX_DEVICES_PER_NODE) { h->err = "node has more devices than HS_MAX_DEVICES_PER_NODE"; return HS_ERR_UNSUPPORTED; }
   std::vector<DevSlot> devs;
   for (uint32_t i = 0; i < node->n_devices; i++) {
@@ -1850,6 +1983,7 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
 
 int32_t hs_node_remove(hs_handle* h, const char* name) {
   if (!h || !name) return HS_ERR_INVALID;
+  HS_IDLE(h);
   auto it = h->node_by_name.find(name);
   if (it == h->node_by_name.end() || !h->nodes[it->second].alive) return HS_ERR_NOTFOUND;
   int slot = it->second;
@@ -1874,6 +2008,7 @@ int32_t hs_node_remove(hs_handle* h, const char* name) {
 int32_t hs_usage_apply(hs_handle* h, const char* pod_uid, const char* node, const char* uuid,
                        int32_t slots, int32_t usedmem, int32_t usedcores) {
   if (!h || !pod_uid || !node || !uuid) return HS_ERR_INVALID;
+  HS_IDLE(h);
   auto it = h->node_by_name.find(node);
   if (it == h->node_by_name.end() || !h->nodes[it->second].alive) return HS_ERR_NOTFOUND;
   int slot = it->second;
@@ -1902,6 +2037,7 @@ int32_t hs_usage_apply(hs_handle* h, const char* pod_uid, const char* node, cons
 
 int32_t hs_pod_delete(hs_handle* h, const char* pod_uid) {
   if (!h || !pod_uid) return HS_ERR_INVALID;
+  HS_IDLE(h);
   auto it = h->pods.find(pod_uid);
   if (it == h->pods.end()) return HS_ERR_NOTFOUND;
   apply_host_delta(h, it->second.node, it->second.delta, -1);
@@ -1916,6 +2052,7 @@ int32_t hs_rollback(hs_handle* h, const char* pod_uid) { return hs_pod_delete(h,
 
 int32_t hs_pod_get(hs_handle* h, const char* pod_uid, const char** node_name, hs_pod_usage_row* rows, uint32_t cap) {
   if (!h || !pod_uid) return HS_ERR_INVALID;
+  HS_IDLE(h);
   auto it = h->pods.find(pod_uid);
   if (it == h->pods.end()) return HS_ERR_NOTFOUND;
   const NodeSlot& ns = h->nodes[it->second.node];
@@ -1933,6 +2070,7 @@ int32_t hs_pod_get(hs_handle* h, const char* pod_uid, const char** node_name, hs
 int32_t hs_filter(hs_handle* h, const hs_pod* pod, const char* const* node_names, uint32_t n_names,
                   hs_filter_result* out) {
   if (!h || !pod || !out) return HS_ERR_INVALID;
+  HS_IDLE(h);
   cudaSetDevice(h->device);
   h->r_strs.clear();
   memset(out, 0, sizeof *out);
@@ -1973,6 +2111,7 @@ static int quota_vendor(hs_handle* h, const char* vendor) {
 }
 int32_t hs_quota_set(hs_handle* h, const char* ns, const char* vendor, int32_t which, int64_t limit) {
   if (!h || !ns || (which != 0 && which != 1)) return HS_ERR_INVALID;
+  HS_IDLE(h);
   const int vid = quota_vendor(h, vendor);
   if (vid < 0) { h->err = "hs_quota_set: unknown vendor (not a managed quota)"; return HS_ERR_NOTFOUND; }
   hs_handle::QuotaEnt& q = h->quota_at(ns, vid);
@@ -1983,6 +2122,7 @@ int32_t hs_quota_set(hs_handle* h, const char* ns, const char* vendor, int32_t w
 }
 int32_t hs_quota_del(hs_handle* h, const char* ns, const char* vendor, int32_t which) {
   if (!h || !ns || (which != 0 && which != 1)) return HS_ERR_INVALID;
+  HS_IDLE(h);
   const int vid = quota_vendor(h, vendor);
   if (vid < 0) return HS_ERR_NOTFOUND;
   hs_handle::QuotaEnt* q = h->quota_find(ns, vid);
@@ -2020,10 +2160,28 @@ int32_t hs_filter_dry(hs_handle* h, const hs_pod* pod, const char* const* node_n
 int32_t hs_run_batch(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
   if (!h || (!ops && n_ops)) return HS_ERR_INVALID;
   cudaSetDevice(h->device);
+  HS_IDLE(h);
   h->have_cand = false;
   int rc = run_ops(h, ops, n_ops);
   if (rc != HS_OK) return rc;
   return (int32_t)n_ops;
+}
+
+int32_t hs_run_batch_async(hs_handle* h, const hs_op* ops, uint32_t n_ops) {
+  if (!h || (!ops && n_ops)) return HS_ERR_INVALID;
+  cudaSetDevice(h->device);
+  HS_IDLE(h);
+  h->have_cand = false;
+  int rc = run_ops(h, ops, n_ops, true);
+  if (rc != HS_OK) return rc;
+  return (int32_t)n_ops;
+}
+
+int32_t hs_batch_wait(hs_handle* h, uint32_t i) {
+  if (!h) return HS_ERR_INVALID;
+  if (i == 0xffffffffu) return job_finish(h);
+  if (i >= h->user_first_op.size()) return HS_ERR_INVALID;
+  return job_wait_user(h, i);
 }
 
 int32_t hs_batch_get(hs_handle* h, uint32_t i, hs_filter_result* out) {
@@ -2031,6 +2189,8 @@ int32_t hs_batch_get(hs_handle* h, uint32_t i, hs_filter_result* out) {
   h->r_strs.clear();
   memset(out, 0, sizeof *out);
   out->node_index = -1;
+  int wrc = job_wait_user(h, i);
+  if (wrc != HS_OK) { out->status = wrc; return wrc; }
   if (h->user_status[i] != HS_OK) { out->status = h->user_status[i]; return out->status; }
   if (h->user_first_op[i] < 0) { out->status = HS_ERR_INVALID; return out->status; }
   assemble_result(h, h->user_first_op[i], out);
@@ -2052,6 +2212,8 @@ int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint6
   for (size_t i = 0; i < h->user_first_op.size(); i++) {
     h->r_strs.clear();
     memset(&r, 0, sizeof r);
+    int wrc = job_wait_user(h, (uint32_t)i);     // a running pipeline: the results of finished chunks are read while it goes on
+    if (wrc != HS_OK) return wrc;
     if (h->user_status[i] != HS_OK) r.status = h->user_status[i];
     else if (h->user_first_op[i] < 0) r.status = HS_ERR_INVALID;
     else if (h->hostprof) {
@@ -2080,8 +2242,10 @@ int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint6
   if (n_fit) *n_fit = fit;
   if (n_nofit) *n_nofit = nofit;
   if (digest) *digest = hsh;
-  h->host_s[3] += now_s() - t0;
-  return HS_OK;
+  const double t1 = now_s();
+  int frc = job_finish(h);
+  h->host_s[3] += t1 - t0;
+  return frc;
 }
 
 /* Measurement hook (no counterpart in the reference): the inventory scan in isolation.  Compiles `pod`, then
@@ -2090,6 +2254,7 @@ int32_t hs_batch_summary(hs_handle* h, uint32_t* n_fit, uint32_t* n_nofit, uint6
  * kernel whose HBM traffic is N x 256 B per launch. */
 int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* ms_avg, int32_t* node_index, float* score) {
   if (!h || !pod || iters == 0) return HS_ERR_INVALID;
+  HS_IDLE(h);
   cudaSetDevice(h->device);
   h->have_cand = false;
   std::vector<uint32_t> uuid_pool;
@@ -2155,12 +2320,14 @@ int64_t hs_debug_metax_table(const char* json, int64_t index) {
 
 int32_t hs_debug_copy_bytes(hs_handle* h, uint64_t out[2]) {
   if (!h) return HS_ERR_INVALID;
+  HS_IDLE(h);
   out[0] = h->bytes_h2d; out[1] = h->bytes_d2h;
   return HS_OK;
 }
 
 int32_t hs_debug_host_seconds(hs_handle* h, double out[4]) {
   if (!h) return HS_ERR_INVALID;
+  HS_IDLE(h);
   for (int i = 0; i < 4; i++) out[i] = h->host_s[i];
   return HS_OK;
 }
@@ -2217,6 +2384,7 @@ int32_t hs_shard_connect(hs_handle* h, const void* handles64, int32_t world) {
 
 int32_t hs_snapshot_node(hs_handle* h, const char* node, hs_device_usage_row* rows, uint32_t cap) {
   if (!h || !node) return HS_ERR_INVALID;
+  HS_IDLE(h);
   auto it = h->node_by_name.find(node);
   if (it == h->node_by_name.end() || !h->nodes[it->second].alive) return HS_ERR_NOTFOUND;
   int slot = it->second;
@@ -2263,6 +2431,7 @@ int32_t hs_debug_window_stats(hs_handle* h, unsigned long long timing16[16], uin
  * one per caller op (0 for ops that are not Filters or never reached the device). */
 int32_t hs_debug_decision_ns(hs_handle* h, uint64_t* out, uint32_t cap) {
   if (!h || !out) return HS_ERR_INVALID;
+  HS_IDLE(h);
   uint32_t n = 0;
   for (size_t i = 0; i < h->user_first_op.size() && n < cap; i++, n++) {
     out[n] = 0;
@@ -2274,7 +2443,7 @@ int32_t hs_debug_decision_ns(hs_handle* h, uint64_t* out, uint32_t cap) {
   return (int32_t)n;
 }
 
-double hs_last_device_ms(const hs_handle* h) { return h ? h->last_ms : 0.0; }
+double hs_last_device_ms(const hs_handle* h) { if (h) job_finish(const_cast<hs_handle*>(h)); return h ? h->last_ms : 0.0; }
 uint64_t hs_launch_count(const hs_handle* h) { return h ? h->launches : 0; }
 
 }  // extern "C"
@@ -2387,6 +2556,7 @@ static unsigned char* g_static_ptr[64] = {nullptr};   // device address of g_sta
 
 extern "C" int32_t hs_sweep_static(hs_handle* h, const hs_pod* pod, void* out_device16, void* cuda_stream) {
   if (!h || !pod || !out_device16) return HS_ERR_INVALID;
+  HS_IDLE(h);
   if (cudaSetDevice(h->device) != cudaSuccess) { h->err = "cudaSetDevice failed"; return HS_ERR_CUDA; }
   if (h->device < 0 || h->device >= 64) { h->err = "device ordinal out of range"; return HS_ERR_UNSUPPORTED; }
   if (!g_static_ptr[h->device]) {

@@ -321,6 +321,7 @@ static __device__ int run_window(const KernelArgs& ka, int r0, int wlen, WinShar
       }
       if (tid == 0) { ka.decisions[r].status = 2; ka.decisions[r].n_alloc = 0; }
       n_exec++;
+      WTICK(15);
       continue;
     }
     if (p.op != OP_FILTER) {
@@ -333,6 +334,7 @@ static __device__ int run_window(const KernelArgs& ka, int r0, int wlen, WinShar
     for (;;) {
       // tracked nodes: exact, on their current registers (whole-CTA call: fast_fit is a warp collective)
       const bool fit = fast_fit(T, glane, (uint32_t)(tnode >= 0 ? tnode : 0), tflags, p, p.e0, ka, fe);
+      WTICK(12);
       unsigned long long key = 0;
       if (tnode >= 0 && fit && (tflags & NF_ALIVE) && glane == 0)
         key = make_key(tpre, spread, (uint32_t)(ka.pos_base + tnode)) | 0x80ull | (unsigned long long)grp;
@@ -340,6 +342,7 @@ static __device__ int run_window(const KernelArgs& ka, int r0, int wlen, WinShar
       const int nt_ = ws.n_tracked;
       for (int t = tid; t < n_tiles; t += blockDim.x) { const unsigned long long h = tile_best(j, t, nt_); key = h > key ? h : key; }
       const unsigned long long best = win_block_max(key, ws);
+      WTICK(13);
       if (!KEY_VALID(best)) { stop = 1; break; }
       if (best & 0x80ull) { win_slot = (int)(best & 31ull); break; }
       if (ws.n_tracked == HS_WSLOTS) { stop = 2; break; }
@@ -377,6 +380,7 @@ static __device__ int run_window(const KernelArgs& ka, int r0, int wlen, WinShar
       if (grp == win_slot) { tpre = sc; if (glane == 0) ka.node_tot[tnode].y = __float_as_int(sc); }
     }
     n_exec++;
+    WTICK(14);
   }
 
   // ---- publish

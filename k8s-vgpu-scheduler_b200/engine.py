@@ -16,7 +16,7 @@ _lib = None
 
 EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
-    "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_batch_get", "hs_rollback",
+    "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_run_batch_async", "hs_batch_wait", "hs_batch_get", "hs_rollback",
     "hs_snapshot_node", "hs_pod_get", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
     "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect",
     "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_filter_dry", "hs_filter_simulate", "hs_quota_set", "hs_quota_del", "hs_quota_get", "hs_quota_memory_factor", "hs_generate_requests", "hs_debug_timing", "hs_debug_window_stats", "hs_debug_decision_ns", "hs_debug_copy_bytes", "hs_debug_host_seconds", "hs_debug_divcheck", "hs_debug_metax_table",
@@ -46,6 +46,8 @@ def lib():
     L.hs_filter_dry.argtypes = [C.c_void_p, P(abi.hs_pod), P(C.c_char_p), C.c_uint32, P(abi.hs_filter_result)]
     L.hs_filter_simulate.argtypes = [C.c_void_p, P(abi.hs_pod), P(abi.hs_sim_node), C.c_uint32, P(abi.hs_filter_result)]
     L.hs_run_batch.argtypes = [C.c_void_p, P(abi.hs_op), C.c_uint32]
+    L.hs_run_batch_async.argtypes = [C.c_void_p, P(abi.hs_op), C.c_uint32]
+    L.hs_batch_wait.argtypes = [C.c_void_p, C.c_uint32]
     L.hs_batch_get.argtypes = [C.c_void_p, C.c_uint32, P(abi.hs_filter_result)]
     L.hs_batch_summary.argtypes = [C.c_void_p, P(C.c_uint32), P(C.c_uint32), P(C.c_uint64)]
     L.hs_shard_unique_id.argtypes = [C.c_void_p]
@@ -259,6 +261,15 @@ class Engine:
     def run_batch(self, packed):
         """packed: PackedOps. Returns number of ops run; results via batch_get(i)."""
         return self._check(self.L.hs_run_batch(self.h, packed.arr, packed.n))
+
+    def run_batch_async(self, packed):
+        """Start the batch and return: results are read with batch_get / batch_summary while later chunks still run.
+        `packed` must stay alive until the batch has finished (batch_wait(), a complete batch_summary, or any other call)."""
+        self._async_keep = packed
+        return self._check(self.L.hs_run_batch_async(self.h, packed.arr, packed.n))
+
+    def batch_wait(self, i=0xFFFFFFFF):
+        return self._check(self.L.hs_batch_wait(self.h, i))
 
     def batch_get(self, i):
         res = abi.hs_filter_result()

@@ -45,7 +45,8 @@ L.hs_debug_window_stats(e.h, t16, st)
 if st[0]:
     print("windows %d (both batches), ops decided in windows %d (%.1f per window), stops: no-fit %d, tracker full %d; winners loaded late %d"
           % (st[0], st[1], st[1] / st[0], st[2], st[3], st[4]))
-    for nm, i in (("whole windows (any CTA 0 view)", 7), ("stage+sweep", 8), ("wait arrivals", 9), ("pre-track", 10), ("ops in order", 11)):
+    for nm, i in (("whole windows (any CTA 0 view)", 7), ("stage+sweep", 8), ("wait arrivals", 9), ("pre-track", 10), ("ops in order: rest", 11),
+                   ("  fit of the tracked nodes", 12), ("  scan + block max", 13), ("  commit + node score", 14), ("  release ops", 15)):
         print("  %-32s %12d clk  %.2f us/window @1.965GHz" % (nm, t16[i], t16[i] / 1965.0 / st[0]))
 L.hs_debug_host_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
 hs = (C.c_double * 4)()
