@@ -879,7 +879,10 @@ int device_begin(hs_handle* h, int max_ops, uint32_t alloc_bound) {
 
 struct StageMark { size_t pods = 0, entries = 0, uuid = 0, rel = 0; };   // how much of each staging array is on the device
 
-int device_range(hs_handle* h, int first, int last, const StageMark& from, const StageMark& to, uint32_t alloc_cap) {
+// with_rows: the collapsed deltas of these ops and their allocation rows [alloc_from, alloc_to) come back together with
+// the decisions (otherwise the caller fetches rows and deltas for the whole batch afterwards, device_end).
+int device_range(hs_handle* h, int first, int last, const StageMark& from, const StageMark& to, uint32_t alloc_cap,
+                 bool with_rows = false, uint32_t alloc_from = 0, uint32_t alloc_to = 0) {
   cudaSetDevice(h->device);               // may run on a helper thread
   const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
   const int n_ops = last;
@@ -899,7 +902,15 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
     if (le != cudaSuccess) { h->err = std::string("hs_decide_kernel launch: ") + cudaGetErrorString(le); return HS_ERR_CUDA; }
     h->launches++;
     CUDA_OK(h, cudaEventRecord(h->ev1, h->stream));
+    // everything the launch produced comes back behind it on the stream, ONE synchronisation for all of it: counters,
+    // the decisions of every op it may have reached (a launch normally runs to the end of its range), their collapsed
+    // deltas and, for a pipelined chunk, its allocation rows
     CUDA_OK(h, down(h, h->b_counters.h, h->b_counters.d, 8 * sizeof(uint32_t)));
+    CUDA_OK(h, down(h, h->b_dec.h + done, h->b_dec.d + done, (size_t)(n_ops - done) * sizeof(DevDecision)));
+    if (with_rows) {
+      CUDA_OK(h, down(h, h->b_delta.h + (size_t)done * HS_D, h->b_delta.d + (size_t)done * HS_D, (size_t)(n_ops - done) * HS_D * sizeof(int4)));
+      if (alloc_to > alloc_from) CUDA_OK(h, down(h, h->b_alloc.h + alloc_from, h->b_alloc.d + alloc_from, (size_t)(alloc_to - alloc_from) * sizeof(DevAlloc)));
+    }
     CUDA_OK(h, cudaStreamSynchronize(h->stream));
     float ms = 0;
     cudaEventElapsedTime(&ms, h->ev0, h->ev1);
@@ -915,8 +926,6 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
       seg = h->fail_segs.back().data();
     }
     if (ran == 0 && nfail == 0 && n_ops - done > 0) { h->err = "decide kernel made no progress"; return HS_ERR_CUDA; }
-    // decisions of this launch
-    CUDA_OK(h, down_sync(h, h->b_dec.h + done, h->b_dec.d + done, (size_t)ran * sizeof(DevDecision)));
     for (uint32_t i = 0; i < ran; i++) {
       DevDecision& d = h->b_dec.h[done + i];
       if (d.status == 1 && d.fail_slot < nfail) h->op_fail_row[done + i] = seg + (size_t)d.fail_slot * n_nodes;
@@ -1423,7 +1432,8 @@ struct BatchJob {
   // pipeline
   struct Chunk { int first = 0, last = 0; StageMark from, to; uint32_t alloc_from = 0, alloc_to = 0; };
   std::vector<Chunk> chunks;
-  uint32_t chunk_ops = 0;
+  std::vector<uint32_t> bounds;   // caller-op boundaries of the chunks: chunk k = [bounds[k], bounds[k+1]); short chunks first,
+                                  // so the device starts early, then the full chunk size
   int n_staged = 0, n_done = 0, n_absorbed = 0;
   bool compile_finished = false, active = false;
   int rc = HS_OK;
@@ -1503,13 +1513,8 @@ void job_device_loop(hs_handle* h, BatchJob* jp) {
     if (k == 0) j.t_first_submit = now_s();
     int rc = HS_OK;
     if (ch.last > ch.first) {
-      rc = device_range(h, ch.first, ch.last, ch.from, ch.to, j.alloc_bound);
       // this chunk's allocation rows and collapsed deltas come back with it: absorb and result assembly need nothing else
-      if (rc == HS_OK && ch.alloc_to > ch.alloc_from &&
-          down_sync(h, h->b_alloc.h + ch.alloc_from, h->b_alloc.d + ch.alloc_from, (size_t)(ch.alloc_to - ch.alloc_from) * sizeof(DevAlloc)) != cudaSuccess) rc = HS_ERR_CUDA;
-      if (rc == HS_OK && down_sync(h, h->b_delta.h + (size_t)ch.first * HS_D, h->b_delta.d + (size_t)ch.first * HS_D,
-                                   (size_t)(ch.last - ch.first) * HS_D * sizeof(int4)) != cudaSuccess) rc = HS_ERR_CUDA;
-      if (rc == HS_ERR_CUDA && h->err.empty()) h->err = "copying a chunk's results back failed";
+      rc = device_range(h, ch.first, ch.last, ch.from, ch.to, j.alloc_bound, true, ch.alloc_from, ch.alloc_to);
     }
     {
       std::lock_guard<std::mutex> lk(j.mu);
@@ -1546,8 +1551,8 @@ void job_compile_loop(hs_handle* h, BatchJob* jp) {
   };
   StageMark uploaded;
   int first = 0;
-  for (uint32_t i0 = 0; i0 < j.n_ops; i0 += j.chunk_ops) {
-    const uint32_t i1 = std::min<uint32_t>(j.n_ops, i0 + j.chunk_ops);
+  for (size_t kb = 0; kb + 1 < j.bounds.size(); kb++) {
+    const uint32_t i0 = j.bounds[kb], i1 = j.bounds[kb + 1];
     const uint32_t alloc_from = j.alloc_cap;
     job_compile_range(h, j, i0, i1);
     int rc = job_stage(h, j, uploaded, wait_idle);
@@ -1597,7 +1602,7 @@ int job_wait_user(hs_handle* h, uint32_t i) {
   BatchJob* jp = h->job.get();
   if (!jp || !jp->active) return HS_OK;
   BatchJob& j = *jp;
-  const int k = (int)(i / j.chunk_ops);
+  const int k = (int)(std::upper_bound(j.bounds.begin(), j.bounds.end(), i) - j.bounds.begin()) - 1;
   std::unique_lock<std::mutex> lk(j.mu);
   j.cv.wait(lk, [&] { return j.n_done > k || j.rc != HS_OK; });
   return j.rc;
@@ -1682,8 +1687,10 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops, bool async = false) 
   }
   int rc = device_begin(h, max_ops, alloc_bound);
   if (rc != HS_OK) return poison(h, rc);
-  j.alloc_bound = alloc_bound; j.max_ops = max_ops; j.chunk_ops = kChunk;
-  j.chunks.reserve((size_t)(n_ops / kChunk + 2));
+  j.alloc_bound = alloc_bound; j.max_ops = max_ops;
+  for (uint32_t at = 0, step = std::max<uint32_t>(kChunk / 4, 1); at < n_ops; at += step, step = std::min(kChunk, step * 2)) j.bounds.push_back(at);
+  j.bounds.push_back(n_ops);
+  j.chunks.reserve(j.bounds.size());
   j.t_begin = t0;
   j.active = true;
   j.t_device = std::thread(job_device_loop, h, &j);
