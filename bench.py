@@ -338,19 +338,27 @@ def run_ours(args):
 
 
 def scan_probe(n_nodes, peak):
-    """The inventory scan in isolation on an inventory larger than L2: hs_sweep_kernel timed with
-    CUDA events by the hs_scan_probe tool (same library).  algorithmic bytes = nodes x 8 x 32 B."""
+    """The inventory scan in isolation on an inventory larger than L2: hs_sweep_kernel timed with CUDA
+    events by the hs_scan_probe tool (same library), on the idle homogeneous inventory AND on a realistic one (C4's
+    vendor / type mix, ~70 % of the devices in use, 2 % unhealthy; requests with a type selector, a UUID list, numa-bind).
+    algorithmic bytes = nodes x 8 x 32 B."""
     exe = os.path.join(ROOT, "k8s-vgpu-scheduler_b200", "hs_scan_probe")
+    out = {"kernel": "hs_sweep_kernel", "nodes": n_nodes, "peak": peak, "unit": "GB/s"}
     try:
-        lines = subprocess.run([exe, str(n_nodes)], capture_output=True, text=True, timeout=300).stdout.strip().splitlines()
-        rows = [json.loads(x) for x in lines]
-        best = rows[0]
-        return {"kernel": "hs_sweep_kernel", "nodes": n_nodes, "inventory_mb": best["inventory_mb"], "ms": best["ms"],
-                "achieved": best["algorithmic_gbps"], "peak": peak, "unit": "GB/s", "frac": round(best["algorithmic_gbps"] / peak, 4),
-                "request": best["request"],
-                "numa_bind_variant_gbps": rows[1]["algorithmic_gbps"] if len(rows) > 1 else None}
+        for key, flag in (("idle", []), ("realistic", ["--realistic"])):
+            lines = subprocess.run([exe] + flag + [str(n_nodes)], capture_output=True, text=True, timeout=600).stdout.strip().splitlines()
+            rows = [json.loads(x) for x in lines]
+            out[key] = [{"request": r["request"], "ms": r["ms"], "achieved": r["algorithmic_gbps"],
+                         "frac": round(r["algorithmic_gbps"] / peak, 4), "fits": r["fits"]} for r in rows]
+            out["inventory_mb"] = rows[0]["inventory_mb"]
+        # the headline scan figure is the REALISTIC inventory's plain request; the idle one stands beside it
+        out["achieved"] = out["realistic"][0]["achieved"]
+        out["frac"] = out["realistic"][0]["frac"]
+        out["ms"] = out["realistic"][0]["ms"]
+        out["request"] = out["realistic"][0]["request"]
     except Exception as ex:  # the probe is an extra; the bench line must still be printed
-        return {"error": str(ex)}
+        out["error"] = str(ex)
+    return out
 
 
 def cpu_baseline(cfg, nodes, pods0, batch, eng, oa, args, local_rank):
