@@ -207,6 +207,12 @@ struct hs_handle {
   int device = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // chained launches of a pipelined batch: results come back on a second stream while the next launch already runs
+  cudaStream_t stream2 = nullptr, stream3 = nullptr;      // results back / request records up
+  cudaEvent_t cu[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ck0[4] = {nullptr, nullptr, nullptr, nullptr}, ck1[4] = {nullptr, nullptr, nullptr, nullptr}, cc[4] = {nullptr, nullptr, nullptr, nullptr};
+  uint32_t* d_chain = nullptr;          // 2 x {ops completed, fail cursor}, alternating between launches (KernelArgs::chain_in/out)
+  uint32_t* h_chain = nullptr;          // pinned staging for resets
   double last_ms = 0;
   uint64_t launches = 0;
   int block = 256;          // threads per CTA of the decide kernel: 8 lanes per node
@@ -1499,30 +1505,164 @@ int job_stage(hs_handle* h, BatchJob& j, StageMark& mark, WaitIdle wait_idle) {
 }
 
 // ---- the pipeline's two threads -------------------------------------------------------------------------------
+// The device side of the pipeline.  Launches are CHAINED: up to two are queued on the stream at any time, each checking
+// on the device that its predecessor reached its first op (KernelArgs::chain_in), so the GPU goes from one chunk to the
+// next without waiting for the host; every launch's results (counters, decisions, deltas, allocation rows) come back
+// on a second stream as soon as it ends, while its successor already runs.  The fail buffer is filled across the
+// launches of a batch (the cursor travels in the chain); a launch that fills it stops early, the ones queued behind it
+// do nothing, and the host drains the buffer and submits the rest again.
 void job_device_loop(hs_handle* h, BatchJob* jp) {
   BatchJob& j = *jp;
   cudaSetDevice(h->device);
-  for (int k = 0;; k++) {
-    BatchJob::Chunk ch;
-    {
-      std::unique_lock<std::mutex> lk(j.mu);
-      j.cv.wait(lk, [&] { return j.n_staged > k || j.compile_finished || j.rc != HS_OK; });
-      if (j.rc != HS_OK || j.n_staged <= k) break;
-      ch = j.chunks[k];
+  const int n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
+  struct Flight { int k, first, last, slot; uint32_t alloc_from, alloc_to; bool last_of_chunk; };
+  std::deque<Flight> inflight;
+  int launch_no = 0, next_submit = 0, slot_no = 0;
+  uint32_t fail_seen = 0;
+  int rc = HS_OK;
+  auto fail = [&](const char* what, cudaError_t e) { h->err = std::string(what) + ": " + cudaGetErrorString(e); rc = HS_ERR_CUDA; };
+#define DEV_OK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fail(#call, e_); return false; } } while (0)
+  auto set_chain = [&](uint32_t ops_done, uint32_t cursor) -> bool {       // what the NEXT launch will read
+    h->h_chain[0] = ops_done; h->h_chain[1] = cursor;
+    DEV_OK(cudaMemcpyAsync(h->d_chain + 2 * (launch_no & 1), h->h_chain, 2 * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    DEV_OK(cudaStreamSynchronize(h->stream));                                // h_chain is reused
+    return true;
+  };
+  const double t_loop0 = now_s();
+  auto submit = [&](const BatchJob::Chunk& ch, int k, int first, bool upload) -> bool {
+    const int slot = slot_no++ & 3;
+    const double ts0 = now_s();
+    struct Done { hs_handle* h; int k; double t0, base; ~Done() { if (h->hostprof) fprintf(stderr, "[hs pipe] submit chunk %d at %.3f ms, took %.3f ms\n", k, 1e3 * (t0 - base), 1e3 * (now_s() - t0)); } } done_{h, k, ts0, t_loop0};
+    // request records go up on their own stream, while the previous launch still runs (copies queued between two
+    // kernels of one stream cost a copy-engine hand-over each); the launch waits for them through an event
+    auto upl = [&](void* dst, const void* src, size_t bytes) { h->bytes_h2d += bytes; return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, h->stream3); };
+    if (upload) {
+      if (ch.to.pods > ch.from.pods) DEV_OK(upl(h->b_pods.d + ch.from.pods, h->b_pods.h + ch.from.pods, (ch.to.pods - ch.from.pods) * sizeof(DevPod)));
+      if (ch.to.entries > ch.from.entries) DEV_OK(upl(h->b_entries.d + ch.from.entries, h->b_entries.h + ch.from.entries, (ch.to.entries - ch.from.entries) * sizeof(DevEntry)));
+      if (ch.to.uuid > ch.from.uuid) DEV_OK(upl(h->b_uuid.d + ch.from.uuid, h->b_uuid.h + ch.from.uuid, (ch.to.uuid - ch.from.uuid) * sizeof(uint32_t)));
+      if (ch.to.rel > ch.from.rel) DEV_OK(upl(h->b_rel.d + ch.from.rel, h->b_rel.h + ch.from.rel, (ch.to.rel - ch.from.rel) * sizeof(int4)));
     }
-    if (k == 0) j.t_first_submit = now_s();
-    int rc = HS_OK;
-    if (ch.last > ch.first) {
-      // this chunk's allocation rows and collapsed deltas come back with it: absorb and result assembly need nothing else
-      rc = device_range(h, ch.first, ch.last, ch.from, ch.to, j.alloc_bound, true, ch.alloc_from, ch.alloc_to);
+    DEV_OK(cudaMemsetAsync(h->b_counters.d + 8 * slot, 0, 8 * sizeof(uint32_t), h->stream3));
+    DEV_OK(cudaEventRecord(h->cu[slot], h->stream3));
+    DEV_OK(cudaStreamWaitEvent(h->stream, h->cu[slot], 0));
+    KernelArgs ka;
+    build_kernel_args(h, ka, ch.last, j.alloc_bound);
+    ka.op_begin = first;
+    ka.counters = h->b_counters.d + 8 * slot;
+    ka.chain_in = h->d_chain + 2 * (launch_no & 1);
+    ka.chain_out = h->d_chain + 2 * ((launch_no + 1) & 1);
+    launch_no++;
+    DEV_OK(cudaEventRecord(h->ck0[slot], h->stream));
+    DEV_OK((cudaError_t)hs_launch_decide(&ka, h->grid_now, h->block, h->stream));
+    h->launches++;
+    DEV_OK(cudaEventRecord(h->ck1[slot], h->stream));
+    // results: behind the kernel, on the second stream
+    DEV_OK(cudaStreamWaitEvent(h->stream2, h->ck1[slot], 0));
+    auto back = [&](void* dst, const void* src, size_t bytes) { h->bytes_d2h += bytes; return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, h->stream2); };
+    DEV_OK(back(h->b_counters.h + 8 * slot, h->b_counters.d + 8 * slot, 8 * sizeof(uint32_t)));
+    DEV_OK(back(h->b_dec.h + first, h->b_dec.d + first, (size_t)(ch.last - first) * sizeof(DevDecision)));
+    DEV_OK(back(h->b_delta.h + (size_t)first * HS_D, h->b_delta.d + (size_t)first * HS_D, (size_t)(ch.last - first) * HS_D * sizeof(int4)));
+    if (ch.alloc_to > ch.alloc_from) DEV_OK(back(h->b_alloc.h + ch.alloc_from, h->b_alloc.d + ch.alloc_from, (size_t)(ch.alloc_to - ch.alloc_from) * sizeof(DevAlloc)));
+    DEV_OK(cudaEventRecord(h->cc[slot], h->stream2));
+    inflight.push_back(Flight{k, first, ch.last, slot, ch.alloc_from, ch.alloc_to, true});
+    return true;
+  };
+  // wait for the oldest launch; returns the op it reached (== f.last unless the fail buffer filled up), -1 on error
+  auto complete = [&](const Flight& f) -> int {
+    cudaError_t e = cudaEventSynchronize(h->cc[f.slot]);
+    if (e != cudaSuccess) { fail("cudaEventSynchronize", e); return -1; }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, h->ck0[f.slot], h->ck1[f.slot]);
+    h->last_ms += ms;
+    if (h->hostprof) fprintf(stderr, "[hs pipe] chunk %d results at %.3f ms, kernel %.3f ms (%d ops)\n", f.k, 1e3 * (now_s() - t_loop0), ms, f.last - f.first);
+    const uint32_t* c = h->b_counters.h + 8 * f.slot;
+    if (c[6]) { h->err = "fused multi-GPU arg-best: a peer rank never arrived"; rc = HS_ERR_CUDA; return -1; }
+    const int reached = c[2] == 0 ? f.first : (int)c[2];     // a launch that found its predecessor short wrote nothing
+    const uint32_t nfail = c[2] == 0 ? fail_seen : c[1];
+    const DevFail* seg = nullptr;
+    if (nfail > fail_seen) {
+      const size_t bytes = (size_t)(nfail - fail_seen) * n_nodes * sizeof(DevFail);
+      h->bytes_d2h += bytes;
+      // (not on stream2: the successor's result copies are already queued there, behind ITS kernel; the launch that
+      // wrote these records has finished, so any stream may read them)
+      e = cudaMemcpyAsync(h->b_fail.h, h->b_fail.d + (size_t)fail_seen * n_nodes, bytes, cudaMemcpyDeviceToHost, h->stream3);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream3);
+      if (e != cudaSuccess) { fail("fail records", e); return -1; }
+      h->fail_segs.emplace_back(h->b_fail.h, h->b_fail.h + (size_t)(nfail - fail_seen) * n_nodes);
+      seg = h->fail_segs.back().data();
     }
+    for (int op = f.first; op < reached; op++) {
+      const DevDecision& d = h->b_dec.h[op];
+      if (d.status == 1 && d.fail_slot >= fail_seen && d.fail_slot < nfail) h->op_fail_row[op] = seg + (size_t)(d.fail_slot - fail_seen) * n_nodes;
+    }
+    fail_seen = nfail;
+    return reached;
+  };
+
+  if (!h->b_counters.ensure(32)) { h->err = "out of memory"; rc = HS_ERR_CUDA; }
+  if (rc == HS_OK) set_chain(0, 0);
+  j.t_first_submit = 0;
+  while (rc == HS_OK) {
+    // keep two launches queued whenever the compile thread has staged that far
+    bool finished = false;
+    while (inflight.size() < 2) {
+      BatchJob::Chunk ch;
+      bool have = false;
+      {
+        std::unique_lock<std::mutex> lk(j.mu);
+        if (inflight.empty()) j.cv.wait(lk, [&] { return j.n_staged > next_submit || j.compile_finished || j.rc != HS_OK; });
+        if (j.rc != HS_OK) { finished = true; break; }
+        if (j.n_staged > next_submit) { ch = j.chunks[next_submit]; have = true; }
+        else if (j.compile_finished && inflight.empty()) { finished = true; break; }
+      }
+      if (!have) break;
+      if (j.t_first_submit == 0) j.t_first_submit = now_s();
+      const int k = next_submit++;
+      if (ch.last > ch.first) { if (!submit(ch, k, ch.first, true)) break; }
+      else inflight.push_back(Flight{k, ch.first, ch.last, -1, 0, 0, true});      // a chunk without device ops
+    }
+    if (finished || rc != HS_OK) break;
+    if (inflight.empty()) continue;
+    Flight f = inflight.front();
+    inflight.pop_front();
+    int reached = f.slot < 0 ? f.last : complete(f);
+    if (reached < 0) break;
+    while (reached < f.last) {
+      // the fail buffer filled up inside this launch: what was queued behind it did nothing.  Drain (done above: every
+      // record up to the cap is on the host), reset the cursor, run the rest of the chunk, then submit the followers again.
+      if (cudaStreamSynchronize(h->stream) != cudaSuccess || cudaStreamSynchronize(h->stream2) != cudaSuccess) { fail("drain", cudaGetLastError()); break; }
+      inflight.clear();
+      next_submit = f.k + 1;
+      fail_seen = 0;
+      if (!set_chain((uint32_t)reached, 0)) break;
+      if (cudaMemsetAsync(h->b_best.d + reached, 0, sizeof(OpSync), h->stream) != cudaSuccess ||
+          cudaMemsetAsync(h->b_best.d + h->sync2_base + reached, 0, sizeof(OpSync), h->stream) != cudaSuccess) { fail("resume", cudaGetLastError()); break; }
+      BatchJob::Chunk ch;
+      { std::lock_guard<std::mutex> lk(j.mu); ch = j.chunks[f.k]; }
+      const int before = reached;
+      if (!submit(ch, f.k, reached, false)) break;
+      Flight g = inflight.front();
+      inflight.pop_front();
+      reached = complete(g);
+      if (reached < 0) break;
+      if (reached == before && fail_seen == 0) { h->err = "decide kernel made no progress"; rc = HS_ERR_CUDA; break; }
+    }
+    if (rc != HS_OK || reached < 0) break;
     {
       std::lock_guard<std::mutex> lk(j.mu);
-      if (rc != HS_OK) j.rc = rc; else j.n_done = k + 1;
+      j.n_done = f.k + 1;
     }
     j.cv.notify_all();
-    if (rc != HS_OK) break;
   }
+#undef DEV_OK
+  cudaStreamSynchronize(h->stream3);      // nothing of this batch is left on the device when the loop ends, whatever ended it
+  cudaStreamSynchronize(h->stream);
+  cudaStreamSynchronize(h->stream2);
+  if (rc != HS_OK) {
+    std::lock_guard<std::mutex> lk(j.mu);
+    j.rc = rc;
+  }
+  j.cv.notify_all();
   j.t_device_done = now_s();
 }
 
@@ -1554,8 +1694,11 @@ void job_compile_loop(hs_handle* h, BatchJob* jp) {
   for (size_t kb = 0; kb + 1 < j.bounds.size(); kb++) {
     const uint32_t i0 = j.bounds[kb], i1 = j.bounds[kb + 1];
     const uint32_t alloc_from = j.alloc_cap;
+    const double tc0 = now_s();
     job_compile_range(h, j, i0, i1);
+    const double tc1 = now_s();
     int rc = job_stage(h, j, uploaded, wait_idle);
+    if (h->hostprof) fprintf(stderr, "[hs pipe] compile chunk %zu: %u ops, compile %.3f ms, stage %.3f ms, staged at %.3f ms\n", kb, i1 - i0, 1e3 * (tc1 - tc0), 1e3 * (now_s() - tc1), 1e3 * (now_s() - j.t_begin));
     BatchJob::Chunk ch;
     ch.first = first; ch.last = (int)j.pods.size(); ch.from = uploaded; ch.to = j.staged;
     ch.alloc_from = alloc_from; ch.alloc_to = j.alloc_cap;
@@ -1568,7 +1711,9 @@ void job_compile_loop(hs_handle* h, BatchJob* jp) {
     if (rc != HS_OK) return;
     uploaded = j.staged;
     first = ch.last;
+    const double ta0 = now_s();
     absorb_ready(false);                        // whatever the device has finished in the meantime
+    if (h->hostprof) fprintf(stderr, "[hs pipe] absorb after chunk %zu: %.3f ms\n", kb, 1e3 * (now_s() - ta0));
     { std::lock_guard<std::mutex> lk(j.mu); if (j.rc != HS_OK) return; }
   }
   { std::lock_guard<std::mutex> lk(j.mu); j.compile_finished = true; }
@@ -1730,6 +1875,16 @@ hs_handle* hs_create(const hs_config* cfg) {
     delete h;
     return nullptr;
   }
+  {
+    bool ok = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&h->stream3, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaMalloc(&h->d_chain, 4 * sizeof(uint32_t)) == cudaSuccess && cudaMallocHost(&h->h_chain, 4 * sizeof(uint32_t)) == cudaSuccess;
+    for (int i = 0; i < 4 && ok; i++)
+      ok = cudaEventCreate(&h->ck0[i]) == cudaSuccess && cudaEventCreate(&h->ck1[i]) == cudaSuccess &&
+           cudaEventCreateWithFlags(&h->cc[i], cudaEventDisableTiming) == cudaSuccess &&
+           cudaEventCreateWithFlags(&h->cu[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) { g_create_error = std::string("hs_create: ") + cudaGetErrorString(cudaGetLastError()); delete h; return nullptr; }
+  }
   add_vendor(h, "NVIDIA", false);
   add_vendor(h, "DCU", false);
   add_vendor(h, "MLU", false);
@@ -1804,6 +1959,11 @@ void hs_destroy(hs_handle* h) {
     if (h->mbox_peer[p] && h->mbox_peer[p] != h->d_mbox) cudaIpcCloseMemHandle(h->mbox_peer[p]);
   if (h->d_mbox) cudaFree(h->d_mbox);
   if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
+  for (int i = 0; i < 4; i++) { if (h->ck0[i]) cudaEventDestroy(h->ck0[i]); if (h->ck1[i]) cudaEventDestroy(h->ck1[i]); if (h->cc[i]) cudaEventDestroy(h->cc[i]); if (h->cu[i]) cudaEventDestroy(h->cu[i]); }
+  if (h->stream3) cudaStreamDestroy(h->stream3);
+  if (h->d_chain) cudaFree(h->d_chain);
+  if (h->h_chain) cudaFreeHost(h->h_chain);
+  if (h->stream2) cudaStreamDestroy(h->stream2);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->stream) cudaStreamDestroy(h->stream);

@@ -300,6 +300,12 @@ hs_decide_kernel(const KernelArgs ka) {
 
   DevAlloc la[HS_MAX_ALLOC];   // general path (lane 0 of the group): picks of the best owned node for the current op
   uint32_t fail_count = 0;     // no-fit decisions so far: identical in every thread
+  if (ka.chain_in != nullptr) {
+    // a launch queued behind its predecessor: it only runs if that one got as far as this one's first op (a launch
+    // that filled the fail buffer stops early; the host drains the buffer and submits the rest again)
+    if (__ldcg(ka.chain_in) != (uint32_t)ka.op_begin) return;     // the same word for every thread of the grid: a uniform exit
+    fail_count = __ldcg(ka.chain_in + 1);
+  }
   uint32_t barriers = 0;       // arg-best exchanges so far in this launch: identical in every thread (and rank)
   int r = ka.op_begin;
   int ring_base = r;           // op whose record sits in s_op[0]: the prefetch ring restarts after every window
@@ -663,7 +669,10 @@ hs_decide_kernel(const KernelArgs ka) {
     my_pre = fast_node_score(D);               // reload means HBM is already current: windows and the general path store it)
     if (dirty && glane == 0 && gg < ka.n_nodes) ka.node_tot[gg].y = __float_as_int(my_pre);
   }
-  if (gtid == 0) { ka.counters[2] = (uint32_t)r; ka.counters[1] = fail_count; ka.counters[5] = barriers; }
+  if (gtid == 0) {
+    ka.counters[2] = (uint32_t)r; ka.counters[1] = fail_count; ka.counters[5] = barriers;
+    if (ka.chain_out != nullptr) { ka.chain_out[0] = (uint32_t)r; ka.chain_out[1] = fail_count; }
+  }
 }
 
 // Sweep-only kernel: evaluates ONE request against the whole inventory and reduces to the arg-best key

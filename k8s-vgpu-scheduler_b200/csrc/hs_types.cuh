@@ -118,8 +118,12 @@ static_assert(sizeof(DevPod) == 160, "DevPod layout: 96 B header + 64 B first en
 
 // numa-bind (nvidia/device.go:770-777) restarts Fit's collection whenever the NUMA id changes along the sorted list.
 // With numa-bind the comparator is numa-major for every policy but "mutex" (policy/gpu_policy.go:101-112,139-147), so
-// each NUMA id is ONE run and the verdict does not depend on the order inside it; only under "mutex" (sorted by Used)
-// does the verdict need the real order.
+// each NUMA id is ONE run and the verdict does not depend on the order inside it.  Under "mutex" (sorted by Used,
+// descending, then NUMA id) the mutex gate only lets idle devices through; those sit together at the tail of the list,
+// grouped by NUMA id, so each NUMA group of idle devices is one run as well and the devices in use before them can only
+// reset a run, never add to it: the verdict is the same per-NUMA count
+// (tests/test_oracle_manual_golden.py::test_numa_bind_verdict_under_mutex_is_a_per_numa_count_too).  Only a topology-aware
+// request under the mutex comparator would need the real order — and the exact policy string "mutex" is never topology-aware.
 #if defined(__CUDACC__)
 #define HS_HD __host__ __device__
 #else
@@ -129,7 +133,8 @@ HS_HD inline bool hs_numa_major(const DevPod& p) {
   return p.sort_mode == SORT_NUMA_BINPACK || p.sort_mode == SORT_NUMA_SPREAD || (p.sort_mode == SORT_CHAIN && p.chain[0] == CK_NUMA);
 }
 HS_HD inline bool hs_verdict_needs_order(const DevPod& p) {
-  return (p.flags & PF_NUMA_ASSERT) && p.e0.vendor == HV_NVIDIA && !hs_numa_major(p);
+  return (p.flags & PF_NUMA_ASSERT) && p.e0.vendor == HV_NVIDIA && !hs_numa_major(p) &&
+         !(p.sort_mode == SORT_MUTEX && !(p.flags & PF_TOPOLOGY));
 }
 
 struct DevAlloc {           // one ContainerDevice, 8 B
@@ -211,5 +216,11 @@ struct KernelArgs {
   uint32_t* w_rmask;            // [tile][HS_WIN]
   unsigned long long* w_head;   // [HS_WIN][n_tiles]
   uint8_t* w_rank;              // [node] rank of the node inside its tile's sorted order
+  // chained launches of one pipelined batch: {ops of the batch completed so far, fail-buffer cursor} as the
+  // predecessor left them (chain_in) and where this launch leaves its own (chain_out; the two alternate, so a CTA that
+  // starts late never reads what its own launch wrote).  A launch whose op_begin differs from chain_in[0] does nothing:
+  // its predecessor stopped early, the host drains the fail buffer and submits the rest again.
+  const uint32_t* chain_in;
+  uint32_t* chain_out;
   uint32_t* w_stats;            // [0] windows, [1] ops decided in windows, [2] stops on no-fit, [3] stops on a full tracker, [4] winners loaded late
 };

@@ -204,6 +204,55 @@ def test_numa_bind_verdict_is_a_per_numa_count_when_the_sort_is_numa_major():
     assert checked[True] > 200 and checked[False] > 200
 
 
+def test_numa_bind_verdict_under_mutex_is_a_per_numa_count_too():
+    """gpu policy "mutex" sorts by Used (descending), so NUMA ids are not contiguous in the list — but the mutex gate lets
+    only idle devices (Used == 0) through, those all sit at the tail of the list, and among equal Used the comparator orders
+    by NUMA id (policy/gpu_policy.go:96-100): the tail is grouped by NUMA, Fit's backward scan meets every NUMA group of
+    idle devices as ONE run, and the devices in use that follow can reset a run but never add to one.  So the verdict is the
+    same per-NUMA count.  (A policy string that names mutex next to something else is a chain, which is numa-major under
+    numa-bind; "topology-aware" never goes with the exact string "mutex".)  Checked against the oracle's sort + Fit."""
+    import ctypes as C
+    import random
+    import oracle_abi as oa
+    from oracle_abi import abi
+    rng = random.Random(31415)
+    orc = oa.Oracle("binpack", "spread")
+    L = orc.L
+    checked = {True: 0, False: 0}
+    for _ in range(2000):
+        nd = rng.randrange(1, 9)
+        devs = []
+        for d in range(nd):
+            devs.append({"ID": "G%d" % d, "Index": d, "Used": rng.choice([0, 0, 0, 1, 3]), "Count": rng.choice([1, 3, 10]), "Usedmem": rng.choice([0, 0, 20000, 70000]),
+                         "Totalmem": 81920, "Totalcore": 100, "Usedcores": rng.choice([0, 0, 30, 100]), "Numa": rng.randrange(0, 4),
+                         "Type": "NVIDIA A100", "Health": rng.random() > 0.15, "Mode": "hami-core"})
+        nums = rng.choice([1, 2, 2, 3, 4])
+        req = {"key": "NVIDIA", "type": "NVIDIA", "nums": nums, "memreq": rng.choice([0, 8192, 30000]), "mempct": 101, "coresreq": rng.choice([0, 30, 100])}
+        if req["memreq"] == 0:
+            req["mempct"] = rng.choice([25, 100])
+        annos = {"hami.io/gpu-scheduler-policy": "mutex", "nvidia.com/numa-bind": "true"}
+        rarr = (abi.hs_container_request * 1)(abi.hs_container_request(b"NVIDIA", b"NVIDIA", req["nums"], req["memreq"], req["mempct"], req["coresreq"]))
+        ctr = abi.hs_container(rarr, 1)
+        p, keep = abi.build_pod({"uid": "p", "ns": "default", "name": "p", "annotations": annos, "containers": [[req]], "n_init": 0})
+        res = abi.hs_filter_result()
+        arr = oa.devs_array([oa.dev_from_go(d) for d in devs])
+        rc = L.oracle_fit_in_devices(orc.h, arr, nd, None, -1, C.byref(ctr), C.byref(p), None, C.byref(res))
+        assert rc in (0, 1), L.oracle_last_error(orc.h)
+
+        def passes(d):
+            memreq = req["memreq"] if req["memreq"] > 0 else d["Totalmem"] * req["mempct"] // 100
+            cores = min(req["coresreq"], 100)
+            return (d["Count"] > d["Used"] and d["Used"] == 0 and d["Totalmem"] - d["Usedmem"] >= memreq and
+                    d["Totalcore"] - d["Usedcores"] >= cores and
+                    not (d["Totalcore"] != 0 and d["Usedcores"] == d["Totalcore"] and cores == 0))
+        reach = [d for d in devs if d["Health"]]
+        want = nums <= nd and any(sum(1 for d in reach if d["Numa"] == v and passes(d)) >= nums for v in range(4))
+        assert (rc == 1) == want, (nums, req, devs)
+        checked[want] += 1
+    orc.close()
+    assert checked[True] > 200 and checked[False] > 200
+
+
 def test_verdict_without_numa_bind_does_not_depend_on_the_device_order():
     """The basis of the sweep's order-free verdict (hs_fast.cuh: fast_fit_lite): without numa-bind a node fits iff at least
     `nums` devices pass every gate, whatever the policy sorts first — checked against the oracle's sort + Fit."""
