@@ -547,6 +547,9 @@ int32_t hs_debug_timing(hs_handle* h, unsigned long long out[8]);
 int32_t hs_debug_window_stats(hs_handle* h, unsigned long long timing16[16], uint32_t stats8[8]);
 /* Cumulative host seconds: request compile, device run + copies, result absorb, summary. */
 int32_t hs_debug_host_seconds(hs_handle* h, double out[4]);
+/* HS_TRACE=1: when every CTA arrived at the barrier of each of the first 512 ops of the last launch (%globaltimer ns),
+ * [ops][stride]: column c = CTA c, column stride-2 = winner's CTA + 1, column stride-1 = CTA 0 saw the barrier complete. */
+int32_t hs_debug_trace(hs_handle* h, uint64_t* out, uint32_t cap, uint32_t* ops, uint32_t* stride);
 /* Cumulative bytes the batch path copied host->device [0] and device->host [1], counted at the copies themselves. */
 int32_t hs_debug_copy_bytes(hs_handle* h, uint64_t out[2]);
 /* The host parser behind hs_node_info.metax_losses / metax_scores on its own (parseMetaxAnnos, metax/device.go:168-183):

@@ -262,6 +262,9 @@ struct hs_handle {
   int w_cap_nodes = 0;
   bool windows = false;                // HS_WINDOW=1: decide runs of common-shape ops in windows (hs_window.cuh); measured slower than the one-op path on C3, so off by default
   DBuf<unsigned long long> b_timing;   // HS_TIMING=1: phase clocks of block 0
+  DBuf<unsigned long long> b_trace;    // HS_TRACE=1: per-op arrival times of every CTA for the first ops of each launch
+  bool trace = false;
+  static constexpr int kTraceOps = 512, kTraceStride = 320;
   bool timing = false;
   // sharded mode (one process per GPU): contiguous node block per rank, NCCL allreduce-max of the packed key per decision
   int shard_rank = 0, shard_world = 1;
@@ -819,6 +822,8 @@ int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_ca
   ka.counters = h->b_counters.d;
   ka.pos_base = (int32_t)h->pos_base;
   ka.timing = h->timing ? h->b_timing.d : nullptr;
+  ka.trace = h->trace ? h->b_trace.d : nullptr;
+  ka.trace_ops = hs_handle::kTraceOps; ka.trace_stride = hs_handle::kTraceStride;
   ka.quota = h->quota_rows.empty() ? nullptr : h->b_quota.d;
   ka.sync2 = h->b_best.d + h->sync2_base;
   ka.world = h->xgpu_connected ? h->shard_world : 1;
@@ -1930,6 +1935,10 @@ hs_handle* hs_create(const hs_config* cfg) {
   h->windows = getenv("HS_WINDOW") != nullptr;
   if (const char* pc = getenv("HS_PIPE_CHUNK")) { if (atoi(pc) > 0) h->pipe_chunk = (uint32_t)atoi(pc); }
   if (getenv("HS_TIMING") && h->b_timing.ensure(16)) { h->timing = true; cudaMemset(h->b_timing.d, 0, 16 * sizeof(unsigned long long)); }
+  if (getenv("HS_TRACE") && h->b_trace.ensure((size_t)hs_handle::kTraceOps * hs_handle::kTraceStride)) {
+    h->trace = true;
+    cudaMemset(h->b_trace.d, 0, (size_t)hs_handle::kTraceOps * hs_handle::kTraceStride * sizeof(unsigned long long));
+  }
   const char* fc = getenv("HS_FAIL_CAP");
   if (fc && atoi(fc) > 0) { h->fail_cap = (uint32_t)atoi(fc); h->fail_cap_fixed = true; }
   if (grow_inventory(h, cfg && cfg->reserve_nodes ? (int)cfg->reserve_nodes : HS_TILE) != HS_OK) {
@@ -1954,7 +1963,7 @@ void hs_destroy(hs_handle* h) {
   if (h->w_stats) cudaFree(h->w_stats);
   h->b_pods.release(); h->b_entries.release(); h->b_uuid.release(); h->b_rel.release(); h->b_dec.release();
   h->b_alloc.release(); h->b_delta.release(); h->b_best.release(); h->b_fail.release(); h->b_counters.release();
-  h->b_candpos.release(); h->b_timing.release(); h->b_quota.release();
+  h->b_candpos.release(); h->b_timing.release(); h->b_trace.release(); h->b_quota.release();
   for (int p = 0; p < 8; p++)        // peer mailboxes opened with cudaIpcOpenMemHandle; our own is a plain allocation
     if (h->mbox_peer[p] && h->mbox_peer[p] != h->d_mbox) cudaIpcCloseMemHandle(h->mbox_peer[p]);
   if (h->d_mbox) cudaFree(h->d_mbox);
@@ -2483,6 +2492,19 @@ int64_t hs_debug_metax_table(const char* json, int64_t index) {
   if (!json || !hs_ingest::decode_int_map(json, m)) return 0;
   for (auto& kv : m) if (kv.first == index) return kv.second;
   return 0;
+}
+
+/* Diagnostic (HS_TRACE=1): the arrival trace of the LAST launch: [ops][stride] ns, see KernelArgs::trace. */
+int32_t hs_debug_trace(hs_handle* h, uint64_t* out, uint32_t cap, uint32_t* ops, uint32_t* stride) {
+  if (!h || !h->trace || !out) return HS_ERR_INVALID;
+  HS_IDLE(h);
+  cudaSetDevice(h->device);
+  const size_t n = (size_t)hs_handle::kTraceOps * hs_handle::kTraceStride;
+  if (cap < n) return HS_ERR_INVALID;
+  if (cudaMemcpy(out, h->b_trace.d, n * sizeof(uint64_t), cudaMemcpyDeviceToHost) != cudaSuccess) return HS_ERR_CUDA;
+  if (ops) *ops = hs_handle::kTraceOps;
+  if (stride) *stride = hs_handle::kTraceStride;
+  return HS_OK;
 }
 
 int32_t hs_debug_copy_bytes(hs_handle* h, uint64_t out[2]) {

@@ -518,11 +518,21 @@ hs_decide_kernel(const KernelArgs ka) {
     unsigned long long win;
     if (ka.world <= 1) {
       slot_arrive(ka.sync + r, bk, s_red);
+      if (ka.trace != nullptr && threadIdx.x == 0 && r - ka.op_begin < ka.trace_ops) {
+        unsigned long long t_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+        ka.trace[(size_t)(r - ka.op_begin) * ka.trace_stride + blockIdx.x] = t_;
+      }
       if (deferred && __any_sync(FULL, my_key != 0ull))     // warp-uniform: fast_fit is a whole-warp collective
         fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
       // (choosing the devices here too, in every group that fits, was measured 8 % SLOWER than leaving fast_pick to
       // the one winner: 5 000 groups pay for it, one benefits)
       win = slot_wait(ka.sync + r, &s_win);
+      if (ka.trace != nullptr && gtid == 0 && r - ka.op_begin < ka.trace_ops) {
+        unsigned long long t_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+        ka.trace[(size_t)(r - ka.op_begin) * ka.trace_stride + ka.trace_stride - 1] = t_;
+      }
     } else {
       win = slot_argbest(ka, ka.sync + r, barriers, bk, s_red, &s_win);
     }
@@ -580,6 +590,8 @@ hs_decide_kernel(const KernelArgs ka) {
           }
           ka.commit_delta[(size_t)r * HS_D + glane] = delta;
           if (glane == 0) {
+            if (ka.trace != nullptr && r - ka.op_begin < ka.trace_ops)
+              ka.trace[(size_t)(r - ka.op_begin) * ka.trace_stride + ka.trace_stride - 2] = (unsigned long long)blockIdx.x + 1ull;
             DevDecision dec;
             dec.status = 0; dec.node = my_node; dec.score = my_score; dec.alloc_off = off; dec.n_alloc = (uint32_t)np;
             dec.fail_slot = 0xffffffffu; stamp_decision(dec);

@@ -216,6 +216,10 @@ struct KernelArgs {
   uint32_t* w_rmask;            // [tile][HS_WIN]
   unsigned long long* w_head;   // [HS_WIN][n_tiles]
   uint8_t* w_rank;              // [node] rank of the node inside its tile's sorted order
+  // diagnostic (HS_TRACE=1): per op of a launch [trace_ops][trace_stride] %globaltimer ns: column c = CTA c's arrival at the
+  // op's barrier, column stride-2 = CTA of the winner (as a number), column stride-1 = when CTA 0 saw the barrier complete
+  unsigned long long* trace;
+  int32_t trace_ops, trace_stride;
   // chained launches of one pipelined batch: {ops of the batch completed so far, fail-buffer cursor} as the
   // predecessor left them (chain_in) and where this launch leaves its own (chain_out; the two alternate, so a CTA that
   // starts late never reads what its own launch wrote).  A launch whose op_begin differs from chain_in[0] does nothing:
