@@ -30,8 +30,8 @@
 #include "hs_ingest.h"
 #include "hs_types.cuh"
 
-extern "C" int hs_launch_decide(const KernelArgs* ka, int grid, int block, cudaStream_t stream);
-extern "C" int hs_decide_max_blocks(int block, int device);
+extern "C" int hs_launch_decide(const KernelArgs* ka, int grid, int block, cudaStream_t stream, int fast_only);
+extern "C" int hs_decide_max_blocks(int block, int device, int fast_only);
 extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int mode, int grid, int block, cudaStream_t stream);
 extern "C" int hs_sweep_blocks_per_sm(int mode);
 extern "C" int hs_launch_shard_decide(const KernelArgs* ka, int op, cudaStream_t stream);
@@ -313,6 +313,8 @@ struct hs_handle {
   uint32_t pipe_chunk = 512;
   int sync2_base = 0;                   // first quota-barrier slot in b_best (== op capacity of the current batch)
   int grid_now = 1;                     // grid of the decide kernel for the current batch
+  int grid_fast = 0;                    // … of its instantiation without the general evaluator (0 = not used: HS_NO_FAST_KERNEL, block != 256)
+  bool fast_kernel = true;
   uint32_t fail_cap_now = 32;           // no-fit decisions one launch can hold before the host drains the reasons
   bool fail_cap_fixed = false;          // HS_FAIL_CAP given: use it as is (tests of the drain-and-resume path)
   std::vector<OpMeta> metas;            // per device op
@@ -879,16 +881,29 @@ int device_begin(hs_handle* h, int max_ops, uint32_t alloc_bound) {
   if (!h->quota_rows.empty())
     CUDA_OK(h, up(h, h->b_quota.d, h->b_quota.h, h->quota_rows.size() * 4 * sizeof(long long)));
   const int block = h->block;
-  const int maxb = hs_decide_max_blocks(block, h->device);
+  const int maxb = hs_decide_max_blocks(block, h->device, 0);
   if (maxb <= 0) { h->err = "hs_decide_kernel cannot be launched cooperatively on this device"; return HS_ERR_CUDA; }
   h->grid_now = std::min(std::min(maxb, 1024), std::max(1, (n_nodes * HS_D + block - 1) / block));   // 8 lanes per node when it fits
+  h->grid_fast = 0;
+  if (h->fast_kernel && block == 256) {
+    const int maxf = hs_decide_max_blocks(block, h->device, 1);
+    if (maxf > 0) h->grid_fast = std::min(std::min(maxf, 1024), std::max(1, (n_nodes * HS_D + block - 1) / block));
+  }
   h->fail_segs.clear();
   h->op_fail_row.assign(max_ops, nullptr);
   h->last_ms = 0;
   return HS_OK;
 }
 
-struct StageMark { size_t pods = 0, entries = 0, uuid = 0, rel = 0; };   // how much of each staging array is on the device
+struct StageMark { size_t pods = 0, entries = 0, uuid = 0, rel = 0; };
+
+// May ops [first, last) run on the instantiation without the general evaluator?  Only common-shape Filters and releases.
+bool range_is_fast(const hs_handle* h, int first, int last) {
+  if (!h->grid_fast) return false;
+  for (int i = first; i < last; i++)
+    if (h->b_pods.h[i].op == OP_FILTER && !h->b_pods.h[i].fast) return false;
+  return true;
+}   // how much of each staging array is on the device
 
 // with_rows: the collapsed deltas of these ops and their allocation rows [alloc_from, alloc_to) come back together with
 // the decisions (otherwise the caller fetches rows and deltas for the whole batch afterwards, device_end).
@@ -909,7 +924,8 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
     build_kernel_args(h, ka, n_ops, alloc_cap);
     ka.op_begin = done;
     CUDA_OK(h, cudaEventRecord(h->ev0, h->stream));
-    cudaError_t le = (cudaError_t)hs_launch_decide(&ka, grid, block, h->stream);
+    const bool fk = range_is_fast(h, done, n_ops);
+    cudaError_t le = (cudaError_t)hs_launch_decide(&ka, fk ? h->grid_fast : grid, block, h->stream, fk ? 1 : 0);
     if (le != cudaSuccess) { h->err = std::string("hs_decide_kernel launch: ") + cudaGetErrorString(le); return HS_ERR_CUDA; }
     h->launches++;
     CUDA_OK(h, cudaEventRecord(h->ev1, h->stream));
@@ -1558,7 +1574,8 @@ void job_device_loop(hs_handle* h, BatchJob* jp) {
     ka.chain_out = h->d_chain + 2 * ((launch_no + 1) & 1);
     launch_no++;
     DEV_OK(cudaEventRecord(h->ck0[slot], h->stream));
-    DEV_OK((cudaError_t)hs_launch_decide(&ka, h->grid_now, h->block, h->stream));
+    const bool fk = range_is_fast(h, first, ch.last);
+    DEV_OK((cudaError_t)hs_launch_decide(&ka, fk ? h->grid_fast : h->grid_now, h->block, h->stream, fk ? 1 : 0));
     h->launches++;
     DEV_OK(cudaEventRecord(h->ck1[slot], h->stream));
     // results: behind the kernel, on the second stream
@@ -1933,6 +1950,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   h->shard_use_nccl = getenv("HS_SHARD_NCCL") != nullptr;
   h->hostprof = getenv("HS_HOSTPROF") != nullptr;
   h->windows = getenv("HS_WINDOW") != nullptr;
+  h->fast_kernel = getenv("HS_NO_FAST_KERNEL") == nullptr;
   if (const char* pc = getenv("HS_PIPE_CHUNK")) { if (atoi(pc) > 0) h->pipe_chunk = (uint32_t)atoi(pc); }
   if (getenv("HS_TIMING") && h->b_timing.ensure(16)) { h->timing = true; cudaMemset(h->b_timing.d, 0, 16 * sizeof(unsigned long long)); }
   if (getenv("HS_TRACE") && h->b_trace.ensure((size_t)hs_handle::kTraceOps * hs_handle::kTraceStride)) {

@@ -266,8 +266,11 @@ __device__ __forceinline__ void stamp_decision(DevDecision& dec) {
   dec.pad[0] = (uint32_t)t; dec.pad[1] = (uint32_t)(t >> 32);
 }
 
-extern "C" __global__ void __launch_bounds__(512, 1)
-hs_decide_kernel(const KernelArgs ka) {
+// GENERAL = false compiles the loop without the general evaluator (hs_eval.cuh): the host launches that instantiation
+// for ranges of ops that are all common-shape Filters and releases — fewer registers, no local-memory frame, and
+// more co-resident CTAs, i.e. a larger register-resident inventory.
+template <bool GENERAL>
+__device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
   __shared__ __align__(16) DevPod s_op[HS_PF];
   __shared__ __align__(16) DevEntry s_ent[HS_MAX_E];
   __shared__ unsigned long long s_red[32];
@@ -298,7 +301,7 @@ hs_decide_kernel(const KernelArgs ka) {
   bool dirty = false;          // usage of the owned node changed: refresh my_pre at the next convergent point
   bool reload = false;         // the general path committed through global memory: re-read the slot
 
-  DevAlloc la[HS_MAX_ALLOC];   // general path (lane 0 of the group): picks of the best owned node for the current op
+  DevAlloc la[GENERAL ? HS_MAX_ALLOC : 1];   // general path (lane 0 of the group): picks of the best owned node for the current op
   uint32_t fail_count = 0;     // no-fit decisions so far: identical in every thread
   if (ka.chain_in != nullptr) {
     // a launch queued behind its predecessor: it only runs if that one got as far as this one's first op (a launch
@@ -414,8 +417,12 @@ hs_decide_kernel(const KernelArgs ka) {
 
     const bool spread = pod.flags & PF_NODE_SPREAD;
     const bool dry = pod.flags & PF_DRYRUN;       // filterSimulation (scheduler.go:1156-1199): decide, do not commit
-    const bool has_quota = ka.quota != nullptr && (pod.q_idx[0] >= 0 || pod.q_idx[1] >= 0);
-    const bool fast = pod.fast != 0;
+    const bool has_quota = GENERAL && ka.quota != nullptr && (pod.q_idx[0] >= 0 || pod.q_idx[1] >= 0);
+    const bool fast = !GENERAL || pod.fast != 0;
+    if (!GENERAL && pod.fast == 0) {          // the host never sends such an op to this instantiation
+      if (gtid == 0) { ka.decisions[r].status = -1; ka.decisions[r].node = -1; ka.decisions[r].n_alloc = 0; }
+      continue;
+    }
     // streaming mode only: in resident mode the full evaluation runs in parallel everywhere, so the winner can
     // commit straight after the barrier (measured: deferring it to the winner lengthens the critical path)
     // Without numa-bind the VERDICT needs no score/sort (fast_fit_lite).  Streaming mode: the winner's warp runs the
@@ -484,7 +491,7 @@ hs_decide_kernel(const KernelArgs ka) {
           node = next; nt = nt2; a = a2; b = b2;
         }
       }
-    } else {
+    } else if constexpr (GENERAL) {
       // general evaluator: one thread (lane 0 of the group) per node
       if (glane == 0) {
         NodeWork w;
@@ -602,7 +609,8 @@ hs_decide_kernel(const KernelArgs ka) {
             if (!resident) { __syncwarp(gmask); if (glane == 0) refresh_node_score(ka, my_node); }
           }
         }
-      } else if (mine) {
+      } else if (GENERAL && mine) {
+        if constexpr (GENERAL) {
         if (glane == 0) {
           int4 delta[HS_D];
           collapse_rows(ent, la, my_nalloc, delta);
@@ -621,6 +629,7 @@ hs_decide_kernel(const KernelArgs ka) {
         }
         __syncwarp(gmask);       // lane 0's stores to the slot rows precede the group's reload
         reload = true;
+        }
       }
       if (has_quota && !dry) {   // the winner changed a namespace's usage: every CTA must see it before the next sweep
         __threadfence();
@@ -647,7 +656,8 @@ hs_decide_kernel(const KernelArgs ka) {
             if (glane == 0) fb[node] = pos >= 0 ? f : nc;
           }
         }
-      } else if (glane == 0) {
+      } else if (GENERAL && glane == 0) {
+        if constexpr (GENERAL) {
         DevFail* fb = ka.fail + (size_t)fail_count * ka.n_nodes;
         NodeWork w;
         EvalOut out;
@@ -664,6 +674,7 @@ hs_decide_kernel(const KernelArgs ka) {
             pack_fail(out, f);
           }
           fb[node] = f;
+        }
         }
       }
       if (gtid == 0) {
@@ -686,6 +697,13 @@ hs_decide_kernel(const KernelArgs ka) {
     if (ka.chain_out != nullptr) { ka.chain_out[0] = (uint32_t)r; ka.chain_out[1] = fail_count; }
   }
 }
+
+extern "C" __global__ void __launch_bounds__(512, 1)
+hs_decide_kernel(const KernelArgs ka) { decide_loop<true>(ka); }
+
+// the same loop without the general evaluator (launched when a range holds only common-shape Filters and releases)
+extern "C" __global__ void __launch_bounds__(256, 3)
+hs_decide_fast_kernel(const KernelArgs ka) { decide_loop<false>(ka); }
 
 // Sweep-only kernel: evaluates ONE request against the whole inventory and reduces to the arg-best key
 // — no commit.  It is the inventory scan measured for the HBM roofline at inventories larger than L2
@@ -966,13 +984,15 @@ extern "C" long long hs_launch_divcheck(unsigned long long n, unsigned long long
 }
 
 // ---- host-callable launch wrappers (kept here so hs_engine.cu stays plain C++) ---------------
-extern "C" int hs_launch_decide(const KernelArgs* ka, int grid, int block, cudaStream_t stream) {
+extern "C" int hs_launch_decide(const KernelArgs* ka, int grid, int block, cudaStream_t stream, int fast_only) {
   void* args[] = {(void*)ka};
-  return (int)cudaLaunchCooperativeKernel((const void*)hs_decide_kernel, dim3(grid), dim3(block), args, 0, stream);
+  return (int)cudaLaunchCooperativeKernel(fast_only ? (const void*)hs_decide_fast_kernel : (const void*)hs_decide_kernel, dim3(grid), dim3(block), args, 0, stream);
 }
-extern "C" int hs_decide_max_blocks(int block, int device) {
+extern "C" int hs_decide_max_blocks(int block, int device, int fast_only) {
   int per_sm = 0, sms = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hs_decide_kernel, block, 0) != cudaSuccess) return 0;
+  cudaError_t e = fast_only ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hs_decide_fast_kernel, block, 0)
+                            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hs_decide_kernel, block, 0);
+  if (e != cudaSuccess) return 0;
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return 0;
   return per_sm * sms;
 }
