@@ -715,8 +715,10 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
   if (!c.entries.empty()) {
     p.e0 = c.entries[0];
     const DevEntry& e = c.entries[0];
+    // Ascend910* (NetworkID groups + ScoreNode) rides the lane-per-device path too (fast_ascend_select); 910C's module
+    // pairing stays with the general evaluator
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
-              !(e.flags & EF_ASCEND910)) ? 1 : 0;
+              !(e.flags & EF_ASCEND910C)) ? 1 : 0;
     if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX | EF_NEURON))) p.fast = 0;
   }
   quota_rows_for(h, c.meta.ns, p);
@@ -1414,7 +1416,7 @@ void mark_windows(std::vector<DevPod>& pods, size_t first) {
   for (size_t i = end; i-- > first;) {
     DevPod& p = pods[i];
     int kind = 0;                                             // 0 not eligible, 1 filter, 2 release / nop
-    if (p.op == OP_FILTER) kind = (p.fast && !(p.flags & PF_DRYRUN)) ? 1 : 0;
+    if (p.op == OP_FILTER) kind = (p.fast && !(p.flags & PF_DRYRUN) && !hs_is_net_scored(p)) ? 1 : 0;
     else if (p.op == OP_RELEASE) kind = (p.q_idx[0] < 0 && p.q_idx[1] < 0) ? 2 : 0;
     else kind = 2;
     if (!kind) { p.win_len = 0; next_len = 0; next_spread = -1; filter_in = 1 << 20; continue; }
@@ -2787,7 +2789,7 @@ extern "C" int32_t hs_sweep_static(hs_handle* h, const hs_pod* pod, void* out_de
   h->quota_rows.clear();            // measurement / scan hook: namespace quotas are not consulted
   if (rc != HS_OK) return rc;
   c.pod.q_idx[0] = c.pod.q_idx[1] = -1;
-  if (!c.pod.fast || c.pod.e0.has_use || c.pod.e0.nouse_cnt) {
+  if (!c.pod.fast || c.pod.e0.has_use || c.pod.e0.nouse_cnt || hs_is_net_scored(c.pod)) {
     h->err = "hs_sweep_static: only the common request shape (one request entry, no UUID use/no-use list) is supported without allocation";
     return HS_ERR_UNSUPPORTED;
   }

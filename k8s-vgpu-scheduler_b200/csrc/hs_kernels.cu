@@ -445,14 +445,18 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
     float my_score = 0.0f;
     uint32_t my_nalloc = 0;
     FastEval fe;
-    fe.cand = 0; fe.q = 0; fe.slot_of = 0; fe.memreq = 0; fe.cores = 0;
+    fe.cand = 0; fe.q = 0; fe.slot_of = 0; fe.memreq = 0; fe.cores = 0; fe.net_topo = false;
+    const bool net_scored = fast && hs_is_net_scored(pod);   // Ascend910*: ScoreNode depends on the picks (fast_ascend_select)
+    int a_row = -1, a_np = 0;
+    float a_term = 0.0f;
     if (fast) {
       if (resident) {
         // whole warp, collectives inside; without numa-bind the verdict needs no score/sort (fast_fit_lite)
         const bool fit = lite ? fast_fit_lite(D, glane, gbase, (uint32_t)gg, my_flags, pod, pod.e0, ka)
                               : fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
+        if (net_scored) a_np = fast_ascend_select(D, glane, gbase, fit, pod.e0, fe, &a_row, &a_term);   // request-level: warp-uniform
         if (fit && my_pos >= 0) {
-          my_score = my_pre;
+          my_score = net_scored ? __fadd_rn(my_pre, a_term) : my_pre;
           my_key = make_key(my_score, spread, (uint32_t)(ka.pos_base + my_pos));
           my_node = gg;
         }
@@ -483,8 +487,10 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
           n.count = b.x; n.totmem = b.y; n.totcore = b.z; n.packed = (uint32_t)b.w;
           const bool fit = (lite ? fast_fit_lite(n, glane, gbase, (uint32_t)node, nf, pod, pod.e0, ka)
                                  : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, f2)) && pos >= 0;
+          float term2 = 0.0f;
+          if (net_scored) { int row2; fast_ascend_select(n, glane, gbase, fit, pod.e0, f2, &row2, &term2); }
           if (fit) {
-            const float sc = __int_as_float(nt.y);
+            const float sc = net_scored ? __fadd_rn(__int_as_float(nt.y), term2) : __int_as_float(nt.y);
             const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
             if (key > my_key) { my_key = key; my_node = node; my_score = sc; }
           }
@@ -570,12 +576,15 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
             my_flags = ka.node_flags[node];
             load_dev(ka, node, glane, D);
           }
-          fast_fit(D, glane, (uint32_t)(my_node >= 0 ? my_node : 0), my_flags, pod, pod.e0, ka, fe);
+          const bool wfit = fast_fit(D, glane, (uint32_t)(my_node >= 0 ? my_node : 0), my_flags, pod, pod.e0, ka, fe);
+          if (net_scored) a_np = fast_ascend_select(D, glane, gbase, wfit, pod.e0, fe, &a_row, &a_term);
         }
         if (mine) {
           // ---- commit: each lane of the winning group commits its own device ------------------
           int my_row;
-          const int np = fast_pick(glane, (uint32_t)my_node, my_flags, pod, pod.e0, ka, fe, &my_row);
+          int np;
+          if (net_scored) { my_row = a_row; np = a_np; }
+          else np = fast_pick(glane, (uint32_t)my_node, my_flags, pod, pod.e0, ka, fe, &my_row);
           const uint32_t off = pod.alloc_base;      // rows of this op: a prefix sum the host made, no cursor atomic
           int4 delta = make_int4(0, 0, 0, 0);
           if (my_row >= 0) {
@@ -766,8 +775,10 @@ hs_sweep_kernel(const KernelArgs ka, int op) {
       n.count = b.x; n.totmem = b.y; n.totcore = b.z; n.packed = (uint32_t)b.w;
       const bool fit = (lite ? fast_fit_lite(n, glane, gbase, (uint32_t)node, nf, pod, pod.e0, ka)
                              : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, fe)) && pos >= 0;
+      float term = 0.0f;
+      if (!lite && hs_is_net_scored(pod)) { int row_; fast_ascend_select(n, glane, gbase, fit, pod.e0, fe, &row_, &term); }
       {
-        const float sc = __int_as_float(nt.y);   // ComputeDefaultScore, maintained by the commits
+        const float sc = __fadd_rn(__int_as_float(nt.y), term);   // ComputeDefaultScore, maintained by the commits (+ Ascend910 ScoreNode)
         if (fit) {
           const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
           my_key = key > my_key ? key : my_key;

@@ -132,7 +132,10 @@ static_assert(sizeof(DevPod) == 160, "DevPod layout: 96 B header + 64 B first en
 HS_HD inline bool hs_numa_major(const DevPod& p) {
   return p.sort_mode == SORT_NUMA_BINPACK || p.sort_mode == SORT_NUMA_SPREAD || (p.sort_mode == SORT_CHAIN && p.chain[0] == CK_NUMA);
 }
+// Ascend910* on the lane-per-device path: the node's rank includes ScoreNode, which depends on the picks
+HS_HD inline bool hs_is_net_scored(const DevPod& p) { return (p.e0.flags & EF_ASCEND910) != 0; }
 HS_HD inline bool hs_verdict_needs_order(const DevPod& p) {
+  if (hs_is_net_scored(p)) return true;
   return (p.flags & PF_NUMA_ASSERT) && p.e0.vendor == HV_NVIDIA && !hs_numa_major(p) &&
          !(p.sort_mode == SORT_MUTEX && !(p.flags & PF_TOPOLOGY));
 }
