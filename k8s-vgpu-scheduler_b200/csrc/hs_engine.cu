@@ -313,6 +313,7 @@ struct hs_handle {
   uint32_t pipe_chunk = 512;
   int sync2_base = 0;                   // first quota-barrier slot in b_best (== op capacity of the current batch)
   int grid_now = 1;                     // grid of the decide kernel for the current batch
+  int maxb_cache[2] = {0, 0}, maxb_block = 0;   // co-resident CTAs of the two decide kernels for `maxb_block` threads (queried once)
   int grid_fast = 0;                    // … of its instantiation without the general evaluator (0 = not used: HS_NO_FAST_KERNEL, block != 256)
   bool fast_kernel = true;
   uint32_t fail_cap_now = 32;           // no-fit decisions one launch can hold before the host drains the reasons
@@ -883,14 +884,15 @@ int device_begin(hs_handle* h, int max_ops, uint32_t alloc_bound) {
   if (!h->quota_rows.empty())
     CUDA_OK(h, up(h, h->b_quota.d, h->b_quota.h, h->quota_rows.size() * 4 * sizeof(long long)));
   const int block = h->block;
-  const int maxb = hs_decide_max_blocks(block, h->device, 0);
+  if (h->maxb_block != block) {
+    h->maxb_cache[0] = hs_decide_max_blocks(block, h->device, 0);
+    h->maxb_cache[1] = (h->fast_kernel && block == 256) ? hs_decide_max_blocks(block, h->device, 1) : 0;
+    h->maxb_block = block;
+  }
+  const int maxb = h->maxb_cache[0];
   if (maxb <= 0) { h->err = "hs_decide_kernel cannot be launched cooperatively on this device"; return HS_ERR_CUDA; }
   h->grid_now = std::min(std::min(maxb, 1024), std::max(1, (n_nodes * HS_D + block - 1) / block));   // 8 lanes per node when it fits
-  h->grid_fast = 0;
-  if (h->fast_kernel && block == 256) {
-    const int maxf = hs_decide_max_blocks(block, h->device, 1);
-    if (maxf > 0) h->grid_fast = std::min(std::min(maxf, 1024), std::max(1, (n_nodes * HS_D + block - 1) / block));
-  }
+  h->grid_fast = h->maxb_cache[1] > 0 ? std::min(std::min(h->maxb_cache[1], 1024), std::max(1, (n_nodes * HS_D + block - 1) / block)) : 0;
   h->fail_segs.clear();
   h->op_fail_row.assign(max_ops, nullptr);
   h->last_ms = 0;
@@ -900,6 +902,12 @@ int device_begin(hs_handle* h, int max_ops, uint32_t alloc_bound) {
 struct StageMark { size_t pods = 0, entries = 0, uuid = 0, rel = 0; };
 
 // May ops [first, last) run on the instantiation without the general evaluator?  Only common-shape Filters and releases.
+// Does any op of [first, last) read the entry pool?  (A pod's first entry rides in its own record.)
+bool range_needs_entries(const hs_handle* h, int first, int last) {
+  for (int i = first; i < last; i++)
+    if (h->b_pods.h[i].op == OP_FILTER && h->b_pods.h[i].n_entries > 1) return true;
+  return false;
+}
 bool range_is_fast(const hs_handle* h, int first, int last) {
   if (!h->grid_fast) return false;
   for (int i = first; i < last; i++)
@@ -916,7 +924,8 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
   const int n_ops = last;
   const int block = h->block, grid = h->grid_now;
   if (to.pods > from.pods) CUDA_OK(h, up(h, h->b_pods.d + from.pods, h->b_pods.h + from.pods, (to.pods - from.pods) * sizeof(DevPod)));
-  if (to.entries > from.entries) CUDA_OK(h, up(h, h->b_entries.d + from.entries, h->b_entries.h + from.entries, (to.entries - from.entries) * sizeof(DevEntry)));
+  if (to.entries > from.entries && range_needs_entries(h, first, last))
+    CUDA_OK(h, up(h, h->b_entries.d + from.entries, h->b_entries.h + from.entries, (to.entries - from.entries) * sizeof(DevEntry)));
   if (to.uuid > from.uuid) CUDA_OK(h, up(h, h->b_uuid.d + from.uuid, h->b_uuid.h + from.uuid, (to.uuid - from.uuid) * sizeof(uint32_t)));
   if (to.rel > from.rel) CUDA_OK(h, up(h, h->b_rel.d + from.rel, h->b_rel.h + from.rel, (to.rel - from.rel) * sizeof(int4)));
   CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
@@ -969,12 +978,6 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
     }
   }
   // (allocation rows sit at each op's own alloc_base, a host-made prefix sum, not behind a device cursor)
-  return HS_OK;
-}
-
-int device_end(hs_handle* h, int n_ops, uint32_t alloc_cap) {
-  if (alloc_cap) CUDA_OK(h, down_sync(h, h->b_alloc.h, h->b_alloc.d, (size_t)alloc_cap * sizeof(DevAlloc)));
-  CUDA_OK(h, down_sync(h, h->b_delta.h, h->b_delta.d, (size_t)n_ops * HS_D * sizeof(int4)));
   return HS_OK;
 }
 
@@ -1561,7 +1564,8 @@ void job_device_loop(hs_handle* h, BatchJob* jp) {
     auto upl = [&](void* dst, const void* src, size_t bytes) { h->bytes_h2d += bytes; return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, h->stream3); };
     if (upload) {
       if (ch.to.pods > ch.from.pods) DEV_OK(upl(h->b_pods.d + ch.from.pods, h->b_pods.h + ch.from.pods, (ch.to.pods - ch.from.pods) * sizeof(DevPod)));
-      if (ch.to.entries > ch.from.entries) DEV_OK(upl(h->b_entries.d + ch.from.entries, h->b_entries.h + ch.from.entries, (ch.to.entries - ch.from.entries) * sizeof(DevEntry)));
+      if (ch.to.entries > ch.from.entries && range_needs_entries(h, ch.first, ch.last))
+        DEV_OK(upl(h->b_entries.d + ch.from.entries, h->b_entries.h + ch.from.entries, (ch.to.entries - ch.from.entries) * sizeof(DevEntry)));
       if (ch.to.uuid > ch.from.uuid) DEV_OK(upl(h->b_uuid.d + ch.from.uuid, h->b_uuid.h + ch.from.uuid, (ch.to.uuid - ch.from.uuid) * sizeof(uint32_t)));
       if (ch.to.rel > ch.from.rel) DEV_OK(upl(h->b_rel.d + ch.from.rel, h->b_rel.h + ch.from.rel, (ch.to.rel - ch.from.rel) * sizeof(int4)));
     }
@@ -1821,8 +1825,7 @@ int run_ops(hs_handle* h, const hs_op* ops, uint32_t n_ops, bool async = false) 
     if (launch_per_op) rc = run_device_ops_sharded(h, n, j.entries.size(), j.uuid_pool.size(), j.rel.size(), j.alloc_cap);
     else {
       rc = device_begin(h, n, j.alloc_cap);
-      if (rc == HS_OK) rc = device_range(h, 0, n, StageMark(), j.staged, j.alloc_cap);
-      if (rc == HS_OK) rc = device_end(h, n, j.alloc_cap);
+      if (rc == HS_OK) rc = device_range(h, 0, n, StageMark(), j.staged, j.alloc_cap, true, 0, j.alloc_cap);   // rows and deltas come back with the decisions
     }
     if (rc != HS_OK) return poison(h, rc);
     const double t2 = now_s();
