@@ -361,6 +361,96 @@ def scan_probe(n_nodes, peak):
     return out
 
 
+def b2_baseline(cfg, nodes, pods0, probe_ops, sample_ops, e2, oa, threads):
+    """B2 of BASELINE.md §3: the lean CPU restatement (oracle/b2_lean.cc — SoA inventory, no strings, no copies, cached node
+    scores, order-free verdict, a persistent thread pool) on the SAME sample from the same pod cache; its decisions (node,
+    score bits, device picks) are compared with the engine's results for the sample.  None when the stream holds request
+    shapes B2 does not handle (type / UUID selectors, other vendors, several containers)."""
+    from k8s_vgpu_scheduler_b200 import abi
+    import struct
+    known = {uid: (node, rows) for uid, node, rows in pods0}
+
+    def compile_ops(ops, index_of):
+        out = []
+        for kind, arg in ops:
+            if kind == "filter":
+                op = oa.b2_compile(arg, cfg)
+                if op is None:
+                    return None
+                index_of[arg["uid"]] = len(out)
+            else:
+                op = oa.b2_op()
+                if arg in index_of:                      # a pod filtered earlier in this stream
+                    op.kind, op.rel_op = 1, index_of.pop(arg)
+                elif arg in known:                       # a pod of the cache the sample started from
+                    node, rows = known.pop(arg)
+                    op.kind, op.rel_node = 2, b2.node_index[node]
+                    for uuid, slots, mem, cores in rows:
+                        d = b2.dev_slot[uuid][1]
+                        op.rel_rows[d][0], op.rel_rows[d][1], op.rel_rows[d][2] = max(slots, 1), mem, cores
+                else:                                    # never held anything
+                    op.kind, op.rel_node = 2, -1
+            out.append(op)
+        return out
+
+    b2 = oa.B2(nodes, threads)
+    try:
+        for uid, node, rows in pods0:
+            for uuid, slots, mem, cores in rows:
+                b2.usage_add(uuid, slots, mem, cores)
+        # the probe ops ran before the sample on the oracle and on the engine: same here (one stream, so in-run releases resolve)
+        stream = compile_ops(list(probe_ops) + list(sample_ops), {})
+        if stream is None:
+            return None
+        n_probe = len(probe_ops)
+        sec_all, out = b2.run(stream)           # the whole stream once: the decisions that are checked
+        b2s = oa.B2(nodes, threads)        # timing: the sample alone, from the state after the probe
+        for uid, node, rows in pods0:
+            for uuid, slots, mem, cores in rows:
+                b2s.usage_add(uuid, slots, mem, cores)
+        b2s.run(stream[:n_probe])
+        rebased = []
+        for op in stream[n_probe:]:
+            if op.kind == 1:
+                if op.rel_op < n_probe:          # releases a probe-phase decision: hand it over as an explicit (node, rows) release
+                    src = out[op.rel_op]
+                    q = oa.b2_op()
+                    q.kind, q.rel_node = 2, src.node
+                    for k in range(src.n_picks):
+                        d = src.picks[k]
+                        q.rel_rows[d][0] += 1; q.rel_rows[d][1] += src.memreq[k]; q.rel_rows[d][2] += src.cores
+                    rebased.append(q)
+                    continue
+                q = oa.b2_op()
+                q.kind, q.rel_op = 1, op.rel_op - n_probe
+                rebased.append(q)
+            else:
+                rebased.append(op)
+        sec, _ = b2s.run(rebased)
+        b2s.close()
+        # decisions of the sample against the engine's
+        slot = b2.dev_slot
+        bad, nfil = 0, 0
+        for i, (kind, arg) in enumerate(sample_ops):
+            if kind != "filter":
+                continue
+            nfil += 1
+            g = e2.batch_get(i)
+            d = out[n_probe + i]
+            if g["status"] == abi.HS_NOFIT:
+                bad += d.node != -1
+                continue
+            rows = next(iter(g["devices"].values()))[0]
+            same = (d.node == b2.node_index[g["node"]] and
+                    struct.pack("f", d.score) == struct.pack("f", g["score"]) and
+                    [slot[r[0]][1] for r in rows] == [d.picks[k] for k in range(d.n_picks)])
+            bad += not same
+        return {"value": round(nfil / sec, 1), "unit": UNIT, "cores": threads, "kind": "port (lean: SoA, no strings, persistent thread pool)",
+                "seconds": round(sec, 3), "filters": nfil, "mismatches_vs_engine": int(bad)}
+    finally:
+        b2.close()
+
+
 def cpu_baseline(cfg, nodes, pods0, batch, eng, oa, args, local_rank):
     """The CPU oracle on a bounded, CONTIGUOUS sample of the first timed batch — filters and deletes — from the very
     pod cache the timed engine had at that point, and the same sample through a second engine handle: the FNV digest
@@ -397,12 +487,13 @@ def cpu_baseline(cfg, nodes, pods0, batch, eng, oa, args, local_rank):
     _, _, d_probe_e = e2.batch_summary()
     e2.run_batch(sample)
     gf, gn, digest_e = e2.batch_summary()
+    b2 = b2_baseline(cfg, nodes, pods0, probe_ops, sample_ops, e2, oa, threads)
     e2.close()
     n_del = sum(1 for kk, _ in sample_ops if kk != "filter")
     return {"value": round(nf2 / sec, 2), "unit": UNIT, "cores": threads, "kind": "port",
             "sample": "%d contiguous ops of the first timed batch (%d filters, %d deletes) from the same pod cache, oracle in "
                       "its lean shape (incremental usage, %d threads over node chunks)" % (len(sample_ops), nf2, n_del, threads),
-            "seconds": round(sec, 2), "filter_ms": round(1e3 * per, 3),
+            "seconds": round(sec, 2), "filter_ms": round(1e3 * per, 3), "b2_lean": b2,
             "parity": {"digest_match": digest_o == digest_e and d_probe_o == d_probe_e, "ops": len(sample_ops) + len(probe_ops),
                        "deletes": n_del, "fits": [nf, gf], "no_fits": [nn, gn]}}
 

@@ -1,0 +1,336 @@
+// b2_lean.cc — TEST / BASELINE INFRASTRUCTURE ONLY (never linked into the product).
+//
+// "B2" of BASELINE.md §3: the strongest honest CPU opponent for the common request shape — the same arithmetic as the
+// reference's Filter/Score path (pkg/scheduler/score.go:81-137,294-346; policy/gpu_policy.go:77-222;
+// policy/node_policy.go:48-130; nvidia/device.go:715-876,887-978) restated the way one would write it for speed on a
+// CPU: structure-of-arrays inventory of integers, no strings, no maps, no per-node copies, incremental usage, the node
+// score cached per node, a verdict that needs no sort for every node and the full sort + scan only for the winner, and
+// a PERSISTENT pool of threads that split the node range (one barrier per decision, no thread is created per decision).
+// It covers what BASELINE configs 1, 2, 3 and 5 send: one container asking NVIDIA for `nums` devices, every gpu policy
+// (binpack / spread / mutex / topology-aware / numa chains), numa-bind, per-pod node policy, scoring weights, releases.
+// Type and UUID selectors, other vendors and multi-container pods are not handled: the oracle (oracle.cc) is the checker
+// for those; B2 is only ever timed next to it and its decisions are compared with the oracle's on the timed sample.
+#include <atomic>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+namespace {
+
+struct B2Node {
+  int32_t used[8], mem[8], cores[8];
+  int32_t count[8], totmem[8], totcore[8];
+  uint8_t numa[8], health[8], type_exact[8];   // type_exact: device Type == "NVIDIA" exactly (ComputeScore's request term)
+  uint8_t ndev, alive, uniform;
+  int16_t pair[64];
+  float score;                                  // ComputeDefaultScore on the current usage
+};
+
+enum { SORT_BINPACK = 0, SORT_SPREAD = 1, SORT_MUTEX = 2, SORT_NUMA_BINPACK = 3, SORT_NUMA_SPREAD = 4, SORT_CHAIN = 5 };
+enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
+
+}  // namespace
+
+extern "C" {
+
+struct b2_op {                // one op of the stream
+  int32_t kind;               // 0 filter, 1 release of `rel_op`'s decision (an earlier op of this run), 2 release of (node, rows)
+  int32_t nums, memreq, mempct, coresreq;
+  uint8_t node_spread, mutex_gate, topology, numa_bind;
+  uint8_t sort_mode, chain[3];
+  float w_slot, w_core, w_mem;
+  int32_t rel_op;             // kind 1
+  int32_t rel_node;           // kind 2
+  int32_t rel_rows[8][3];     // kind 2: {slots, mem, cores} per device
+};
+struct b2_decision {
+  int32_t node;               // -1 = no node fits
+  float score;
+  int32_t n_picks;
+  int8_t picks[8];            // device slots in the order Fit returns them
+  int32_t memreq[8];
+  int32_t cores;
+};
+
+}  // extern "C"
+
+namespace {
+
+struct B2 {
+  std::vector<B2Node> nodes;
+  int threads = 1;
+  // persistent pool
+  std::vector<std::thread> pool;
+  std::atomic<int> phase{0};
+  std::atomic<int> arrived{0};
+  std::atomic<bool> quit{false};
+  const b2_op* cur = nullptr;
+  std::vector<uint64_t> part_key;
+  std::vector<b2_decision> out;
+};
+
+inline float node_score(const B2Node& n) {      // node_policy.go:106-130
+  int32_t used = 0, uc = 0, um = 0, tot = 0, tc = 0, tm = 0;
+  for (int d = 0; d < n.ndev; d++) { used += n.used[d]; uc += n.cores[d]; um += n.mem[d]; tot += n.count[d]; tc += n.totcore[d]; tm += n.totmem[d]; }
+  if (tot == 0 || tc == 0 || tm == 0) return 0.0f;
+  volatile float a = (float)used / (float)tot, b = (float)uc / (float)tc, c = (float)um / (float)tm;
+  volatile float s1 = a + b;
+  volatile float s2 = s1 + c;
+  return 10.0f * s2;
+}
+
+inline uint64_t make_key(float score, bool spread, uint32_t pos) {
+  if (score == 0.0f) score = 0.0f;
+  uint32_t u;
+  memcpy(&u, &score, 4);
+  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  if (spread) u = ~u;
+  return ((uint64_t)u << 32) | (uint64_t)(pos + 1u);
+}
+
+inline int resolve_mem(const b2_op& p, int32_t totmem) {
+  if (p.memreq > 0) return p.memreq;
+  if (p.mempct != 101) return (int32_t)((uint32_t)totmem * (uint32_t)p.mempct) / 100;
+  return 0;
+}
+
+inline bool dev_ok(const B2Node& n, int d, const b2_op& p, int cores) {     // nvidia/device.go:729-811, after the numa check
+  const int memreq = resolve_mem(p, n.totmem[d]);
+  if (n.count[d] <= n.used[d]) return false;
+  if (p.mutex_gate && n.used[d] > 0) return false;
+  if (n.totmem[d] - n.mem[d] < memreq) return false;
+  if (n.totcore[d] - n.cores[d] < cores) return false;
+  if (n.totcore[d] == 100 && cores == 100 && n.used[d] > 0) return false;
+  if (n.totcore[d] != 0 && n.cores[d] == n.totcore[d] && cores == 0) return false;
+  return true;
+}
+
+// Does the node fit?  No sort: without numa-bind `nums` passing devices, with it some NUMA id holding that many (the
+// group at the head of the list for topology-aware) — the per-NUMA rule the engine's tests check against the reference order.
+inline bool verdict(const B2Node& n, const b2_op& p) {
+  if (!n.alive || p.nums > n.ndev) return false;
+  const int cores = p.coresreq > 100 ? 100 : p.coresreq;
+  int okc[8], pre_numa_min = 256, pre_numa_max = -1, total = 0;
+  for (int d = 0; d < n.ndev; d++) {
+    okc[d] = 0;
+    if (!n.health[d]) continue;
+    if (n.numa[d] < pre_numa_min) pre_numa_min = n.numa[d];
+    if (n.numa[d] > pre_numa_max) pre_numa_max = n.numa[d];
+    if (dev_ok(n, d, p, cores)) { okc[d] = 1; total++; }
+  }
+  if (!p.numa_bind) return total >= p.nums;
+  if (p.topology) {
+    const int head = p.sort_mode == SORT_NUMA_BINPACK ? pre_numa_max : pre_numa_min;
+    int c = 0;
+    for (int d = 0; d < n.ndev; d++) if (okc[d] && n.numa[d] == head) c++;
+    return c >= p.nums;
+  }
+  for (int d = 0; d < n.ndev; d++) {
+    if (!okc[d]) continue;
+    int c = 0;
+    for (int k = 0; k < n.ndev; k++) if (okc[k] && n.numa[k] == n.numa[d]) c++;
+    if (c >= p.nums) return true;
+  }
+  return false;
+}
+
+inline float dev_score(const B2Node& n, int d, const b2_op& p) {           // gpu_policy.go:194-222
+  if (n.count[d] == 0 || n.totcore[d] == 0 || n.totmem[d] == 0) return 0.0f;
+  int req = 0, core = 0, mem = 0;
+  if (n.type_exact[d]) {
+    req = 1; core = p.coresreq;
+    if (p.mempct != 0 && p.mempct != 101) mem = (int32_t)(((int64_t)n.totmem[d] * (int64_t)p.mempct) / 100);
+    else mem = p.memreq;
+  }
+  volatile float us = (float)(req + n.used[d]) / (float)n.count[d];
+  volatile float cs = (float)(core + n.cores[d]) / (float)n.totcore[d];
+  volatile float ms = (float)(mem + n.mem[d]) / (float)n.totmem[d];
+  volatile float a = p.w_slot * us, b = p.w_core * cs, c = p.w_mem * ms;
+  volatile float s1 = a + b;
+  volatile float s2 = s1 + c;
+  return 10.0f * s2;
+}
+
+// Less (gpu_policy.go:77-167) on (score, numa, used, index)
+inline bool less_dev(const b2_op& p, float sa, int na, int ua, int ia, float sb, int nb, int ub, int ib) {
+  switch (p.sort_mode) {
+    case SORT_BINPACK: if (sa != sb) return sa < sb; return na < nb;
+    case SORT_SPREAD: if (sa != sb) return sa > sb; return na < nb;
+    case SORT_MUTEX: if (ua != ub) return ua > ub; return na < nb;
+    case SORT_NUMA_BINPACK: if (na != nb) return na > nb; return sa < sb;
+    case SORT_NUMA_SPREAD: if (na != nb) return na < nb; return sa > sb;
+    default:
+      for (int i = 0; i < 3; i++) {
+        const int k = p.chain[i];
+        if (k == CK_BINPACK) { if (sa != sb) return sa < sb; }
+        else if (k == CK_SPREAD) { if (sa != sb) return sa > sb; }
+        else if (k == CK_NUMA) { if (na != nb) return na < nb; }
+      }
+      return ia < ib;
+  }
+}
+
+// The winner's Fit: sort (stable insertion, like Go's sort.Sort for n <= 12), backward scan, topology choice
+bool full_fit(const B2Node& n, const b2_op& p, b2_decision& out) {
+  const int cores = p.coresreq > 100 ? 100 : p.coresreq;
+  int order[8];
+  float sc[8];
+  for (int d = 0; d < n.ndev; d++) { order[d] = d; sc[d] = dev_score(n, d, p); }
+  for (int i = 1; i < n.ndev; i++)
+    for (int j = i; j > 0; j--) {
+      const int a = order[j], b = order[j - 1];
+      if (!less_dev(p, sc[a], n.numa[a], n.used[a], a, sc[b], n.numa[b], n.used[b], b)) break;
+      order[j] = b; order[j - 1] = a;
+    }
+  int tmp[8], ntmp = 0, prev = -1, left = p.nums;
+  for (int i = n.ndev - 1; i >= 0; i--) {
+    const int d = order[i];
+    if (!n.health[d]) continue;
+    if (p.numa_bind && prev != n.numa[d]) { left = p.nums; prev = n.numa[d]; ntmp = 0; }
+    if (!dev_ok(n, d, p, cores)) continue;
+    if (left > 0) { if (!p.topology) left--; tmp[ntmp++] = d; }
+    if (left == 0 && !p.topology) break;
+  }
+  if (!p.topology) { if (left != 0) return false; }
+  else {
+    if (ntmp < p.nums) return false;
+    if (ntmp > p.nums && !n.uniform) {
+      if (p.nums == 1) {                                  // computeWorstSingleCard
+        int best = 0, worst = 0; bool have = false;
+        for (int a = 0; a < ntmp; a++) {
+          int total = 0;
+          for (int b = 0; b < ntmp; b++) if (b != a) total += n.pair[tmp[a] * 8 + tmp[b]];
+          if (!have || total < worst) { have = true; worst = total; best = a; }
+        }
+        tmp[0] = tmp[best]; ntmp = 1;
+      } else {                                            // generateCombinations + computeBestCombination
+        uint32_t bestMask = 0; int bestScore = 0; bool have = false;
+        // lexicographic order over index lists == enumerate masks whose lowest differing bit decides; do it by recursion-free walk
+        int idx[8];
+        for (int i = 0; i < p.nums; i++) idx[i] = i;
+        for (;;) {
+          int total = 0;
+          for (int a = 0; a < p.nums; a++) for (int b = a + 1; b < p.nums; b++) total += n.pair[tmp[idx[a]] * 8 + tmp[idx[b]]];
+          if (!have || total > bestScore) { have = true; bestScore = total; bestMask = 0; for (int a = 0; a < p.nums; a++) bestMask |= 1u << idx[a]; }
+          int i = p.nums - 1;
+          while (i >= 0 && idx[i] == ntmp - p.nums + i) i--;
+          if (i < 0) break;
+          idx[i]++;
+          for (int k = i + 1; k < p.nums; k++) idx[k] = idx[k - 1] + 1;
+        }
+        int k = 0;
+        for (int a = 0; a < ntmp; a++) if ((bestMask >> a) & 1u) tmp[k++] = tmp[a];
+        ntmp = k;
+      }
+    } else if (ntmp > p.nums) ntmp = p.nums;              // uniform pair scores: the first `nums` win every strict comparison
+  }
+  out.n_picks = ntmp;
+  out.cores = cores;
+  for (int i = 0; i < ntmp; i++) { out.picks[i] = (int8_t)tmp[i]; out.memreq[i] = resolve_mem(p, n.totmem[tmp[i]]); }
+  return true;
+}
+
+void worker(B2* h, int tid) {
+  int seen = 0;
+  const size_t n = h->nodes.size();
+  const size_t lo = n * (size_t)tid / (size_t)h->threads, hi = n * (size_t)(tid + 1) / (size_t)h->threads;
+  for (;;) {
+    while (h->phase.load(std::memory_order_acquire) == seen) { if (h->quit.load(std::memory_order_relaxed)) return; }
+    seen++;
+    const b2_op& p = *h->cur;
+    uint64_t best = 0;
+    for (size_t i = lo; i < hi; i++) {
+      const B2Node& nd = h->nodes[i];
+      if (verdict(nd, p)) { const uint64_t k = make_key(nd.score, p.node_spread, (uint32_t)i); if (k > best) best = k; }
+    }
+    h->part_key[(size_t)tid * 8] = best;          // one cache line per thread
+    h->arrived.fetch_add(1, std::memory_order_release);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+void* b2_create(int32_t n_nodes, int32_t threads) {
+  B2* h = new B2();
+  h->nodes.resize((size_t)n_nodes);
+  for (auto& n : h->nodes) memset(&n, 0, sizeof n);
+  h->threads = threads < 1 ? 1 : threads;
+  h->part_key.assign((size_t)h->threads * 8, 0);
+  return h;
+}
+void b2_destroy(void* hv) {
+  B2* h = (B2*)hv;
+  h->quit.store(true);
+  for (auto& t : h->pool) t.join();
+  delete h;
+}
+// dev: {count, totmem, totcore, numa, health, type_exact}; pair: 64 int16 or NULL
+void b2_node_set(void* hv, int32_t node, int32_t ndev, const int32_t* dev6, const int16_t* pair) {
+  B2Node& n = ((B2*)hv)->nodes[(size_t)node];
+  n.ndev = (uint8_t)ndev; n.alive = 1;
+  bool uniform = true, have = false; int uval = 0;
+  for (int d = 0; d < ndev; d++) {
+    n.count[d] = dev6[d * 6 + 0]; n.totmem[d] = dev6[d * 6 + 1]; n.totcore[d] = dev6[d * 6 + 2];
+    n.numa[d] = (uint8_t)dev6[d * 6 + 3]; n.health[d] = (uint8_t)dev6[d * 6 + 4]; n.type_exact[d] = (uint8_t)dev6[d * 6 + 5];
+  }
+  for (int i = 0; i < 64; i++) n.pair[i] = pair ? pair[i] : 0;
+  for (int i = 0; i < ndev; i++) for (int j = 0; j < ndev; j++) if (i != j) { const int v = n.pair[i * 8 + j]; if (!have) { have = true; uval = v; } else if (v != uval) uniform = false; }
+  n.uniform = uniform;
+  n.score = node_score(n);
+}
+void b2_usage_add(void* hv, int32_t node, int32_t dev, int32_t slots, int32_t mem, int32_t cores) {
+  B2Node& n = ((B2*)hv)->nodes[(size_t)node];
+  n.used[dev] += slots; n.mem[dev] += mem; n.cores[dev] += cores;
+  n.score = node_score(n);
+}
+
+// Runs the ops in order; returns seconds.  Decisions of filter ops go to out[i].
+double b2_run(void* hv, const b2_op* ops, int32_t n_ops, b2_decision* out) {
+  B2* h = (B2*)hv;
+  if (h->pool.empty() && h->threads > 1)
+    for (int t = 1; t < h->threads; t++) h->pool.emplace_back(worker, h, t);
+  const auto t0 = std::chrono::steady_clock::now();
+  const size_t n = h->nodes.size();
+  const size_t hi0 = n / (size_t)h->threads;
+  for (int32_t i = 0; i < n_ops; i++) {
+    const b2_op& p = ops[i];
+    b2_decision& dec = out[i];
+    dec.node = -1; dec.n_picks = 0; dec.score = 0;
+    if (p.kind != 0) {
+      int node = p.kind == 2 ? p.rel_node : out[p.rel_op].node;
+      if (node >= 0) {
+        B2Node& nd = h->nodes[(size_t)node];
+        if (p.kind == 2) for (int d = 0; d < 8; d++) { nd.used[d] -= p.rel_rows[d][0]; nd.mem[d] -= p.rel_rows[d][1]; nd.cores[d] -= p.rel_rows[d][2]; }
+        else { const b2_decision& f = out[p.rel_op]; for (int k = 0; k < f.n_picks; k++) { const int d = f.picks[k]; nd.used[d] -= 1; nd.mem[d] -= f.memreq[k]; nd.cores[d] -= f.cores; } }
+        nd.score = node_score(nd);
+      }
+      continue;
+    }
+    h->cur = &p;
+    h->arrived.store(0, std::memory_order_relaxed);
+    h->phase.fetch_add(1, std::memory_order_release);
+    uint64_t best = 0;
+    for (size_t k = 0; k < hi0; k++) {                   // the calling thread is worker 0
+      const B2Node& nd = h->nodes[k];
+      if (verdict(nd, p)) { const uint64_t key = make_key(nd.score, p.node_spread, (uint32_t)k); if (key > best) best = key; }
+    }
+    while (h->arrived.load(std::memory_order_acquire) < h->threads - 1) {}
+    for (int t = 1; t < h->threads; t++) if (h->part_key[(size_t)t * 8] > best) best = h->part_key[(size_t)t * 8];
+    if (!best) continue;
+    const uint32_t pos = (uint32_t)(best & 0xffffffffu) - 1u;
+    B2Node& nd = h->nodes[pos];
+    dec.score = nd.score;
+    if (!full_fit(nd, p, dec)) { dec.node = -2; continue; }   // verdict and Fit disagree: must not happen
+    dec.node = (int32_t)pos;
+    for (int k = 0; k < dec.n_picks; k++) { const int d = dec.picks[k]; nd.used[d] += 1; nd.mem[d] += dec.memreq[k]; nd.cores[d] += dec.cores; }
+    nd.score = node_score(nd);
+  }
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+}  // extern "C"

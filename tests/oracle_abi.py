@@ -29,7 +29,7 @@ def lib():
     if _lib is not None:
         return _lib
     so = os.path.join(ROOT, "oracle", "liboracle.so")
-    srcs = [os.path.join(ROOT, "oracle", f) for f in ("oracle.cc", "oracle_capi.cc", "oracle.h", "oracle_capi.h")]
+    srcs = [os.path.join(ROOT, "oracle", f) for f in ("oracle.cc", "oracle_capi.cc", "b2_lean.cc", "oracle.h", "oracle_capi.h")]
     srcs.append(os.path.join(ROOT, "include", "hami_sched.h"))
     if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs if os.path.exists(s)):
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "-s"])
@@ -166,3 +166,110 @@ class Oracle:
         rows = (abi.hs_device_usage_row * cap)()
         n = self.L.oracle_snapshot_node(self.h, abi._b(node), rows, cap)
         return [(rows[i].used, rows[i].usedmem, rows[i].usedcores) for i in range(min(n, cap))]
+
+
+# ---- B2: the lean CPU baseline (oracle/b2_lean.cc) -----------------------------------------------------------
+class b2_op(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("nums", C.c_int32), ("memreq", C.c_int32), ("mempct", C.c_int32), ("coresreq", C.c_int32),
+                ("node_spread", C.c_uint8), ("mutex_gate", C.c_uint8), ("topology", C.c_uint8), ("numa_bind", C.c_uint8),
+                ("sort_mode", C.c_uint8), ("chain", C.c_uint8 * 3), ("w_slot", C.c_float), ("w_core", C.c_float), ("w_mem", C.c_float),
+                ("rel_op", C.c_int32), ("rel_node", C.c_int32), ("rel_rows", (C.c_int32 * 3) * 8)]
+
+
+class b2_decision(C.Structure):
+    _fields_ = [("node", C.c_int32), ("score", C.c_float), ("n_picks", C.c_int32), ("picks", C.c_int8 * 8),
+                ("memreq", C.c_int32 * 8), ("cores", C.c_int32)]
+
+
+def _policy_contains(policy, name):
+    return any(p.strip() == name for p in policy.split(","))
+
+
+def b2_compile(pod, cfg):
+    """The part of Filter that looks at the pod only (util.go:277-298, scheduler.go:641-652, gpu_policy.go:77-167), for the
+    request shape B2 handles; None when the pod is outside it."""
+    an = pod.get("annotations") or {}
+    ctrs = pod["containers"]
+    if len(ctrs) != 1 or len(ctrs[0]) != 1 or pod.get("n_init", 0) or ctrs[0][0]["type"] != "NVIDIA":
+        return None
+    if any(k in an for k in ("hami.io/device-scoring-weights", "nvidia.com/use-gputype", "nvidia.com/nouse-gputype",
+                             "nvidia.com/use-gpuuuid", "nvidia.com/nouse-gpuuuid", "nvidia.com/vgpu-mode")):
+        return None
+    r = ctrs[0][0]
+    gpu = an.get("hami.io/gpu-scheduler-policy", cfg.get("gpu_policy") or "spread")
+    node = an.get("hami.io/node-scheduler-policy", cfg.get("node_policy") or "binpack")
+    numa = an.get("nvidia.com/numa-bind") in ("1", "t", "T", "TRUE", "true", "True")
+    op = b2_op()
+    op.kind, op.nums, op.memreq, op.mempct, op.coresreq = 0, r["nums"], r["memreq"], r["mempct"], r["coresreq"]
+    op.node_spread = 1 if node == "spread" else 0
+    op.mutex_gate = 1 if _policy_contains(gpu, "mutex") else 0
+    op.topology = 1 if _policy_contains(gpu, "topology-aware") else 0
+    op.numa_bind = 1 if numa else 0
+    op.w_slot = op.w_core = op.w_mem = 1.0
+    if "," in gpu or gpu == "numa":
+        op.sort_mode = 5
+        chain, seen = [], set()
+        for t in gpu.split(","):
+            k = {"binpack": 1, "spread": 2, "numa": 3}.get(t.strip(), 0)
+            if k and k not in seen:
+                chain.append(k)
+                seen.add(k)
+        if not chain:
+            chain = [2]
+        if numa and chain[0] != 3:
+            chain = [3] + [k for k in chain if k != 3]
+        for i in range(3):
+            op.chain[i] = chain[i] if i < len(chain) else 0
+    elif gpu == "mutex":
+        op.sort_mode = 2
+    elif numa:
+        op.sort_mode = 3 if gpu == "binpack" else 4
+    else:
+        op.sort_mode = 0 if gpu == "binpack" else 1
+    return op
+
+
+class B2:
+    """Thin wrapper over oracle/b2_lean.cc: SoA inventory, persistent thread pool."""
+
+    def __init__(self, nodes, threads):
+        self.L = lib()
+        self.L.b2_create.restype = C.c_void_p
+        self.L.b2_create.argtypes = [C.c_int32, C.c_int32]
+        self.L.b2_destroy.argtypes = [C.c_void_p]
+        self.L.b2_node_set.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int16)]
+        self.L.b2_usage_add.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+        self.L.b2_run.restype = C.c_double
+        self.L.b2_run.argtypes = [C.c_void_p, C.POINTER(b2_op), C.c_int32, C.POINTER(b2_decision)]
+        self.h = self.L.b2_create(len(nodes), threads)
+        self.node_index = {n["name"]: i for i, n in enumerate(nodes)}
+        self.dev_slot = {}
+        for i, n in enumerate(nodes):
+            devs = n["devices"]
+            arr = (C.c_int32 * (6 * len(devs)))()
+            for d, dv in enumerate(devs):
+                arr[d * 6:d * 6 + 6] = [dv["count"], dv["devmem"], dv["devcore"], dv.get("numa", 0), 1 if dv.get("health", True) else 0,
+                                        1 if dv["type"] == "NVIDIA" else 0]
+                self.dev_slot[dv["id"]] = (i, d)
+            pair = None
+            if n.get("pair_scores"):
+                pair = (C.c_int16 * 64)()
+                for a, row in enumerate(n["pair_scores"]):
+                    for b, v in enumerate(row):
+                        pair[a * 8 + b] = v
+            self.L.b2_node_set(self.h, i, len(devs), arr, pair)
+
+    def usage_add(self, uuid, slots, mem, cores):
+        i, d = self.dev_slot[uuid]
+        self.L.b2_usage_add(self.h, i, d, max(slots, 1), mem, cores)
+
+    def run(self, ops):
+        arr = (b2_op * max(len(ops), 1))(*ops)
+        out = (b2_decision * max(len(ops), 1))()
+        sec = self.L.b2_run(self.h, arr, len(ops), out)
+        return sec, out
+
+    def close(self):
+        if self.h:
+            self.L.b2_destroy(self.h)
+            self.h = None

@@ -243,3 +243,52 @@ def test_streaming_mode_numa_bind():
     cfg, nodes, ops = _gen().config3(n_nodes=10000, n_pods=70)     # > 9 472 resident groups; the oracle needs ~50 s for it
     assert sum(1 for k, a in ops if k == "filter" and a["annotations"].get("nvidia.com/numa-bind") == "true") > 10
     _check(cfg, nodes, ops)
+
+
+def test_ascend910_networkid_groups_on_the_lane_per_device_path():
+    """Ascend910* pods take the lane-per-device path: NetworkID groups of unequal size, devices without a NetworkID (then
+    Fit does not collect, it takes the first fitting devices), nums == 1, hami-core mode, partly used and unhealthy cards —
+    node choice includes ScoreNode (10 x largest picked group / picks), so every fitting node's picks matter."""
+    import random
+    rng = random.Random(910)
+    nodes = []
+    for i in range(120):
+        nd = rng.choice([4, 6, 8, 8])
+        style = rng.random()
+        devs = []
+        for d in range(nd):
+            if style < 0.15:
+                net = -1                                        # no NetworkID anywhere on the node
+            elif style < 0.3:
+                net = -1 if rng.random() < 0.3 else rng.randrange(0, 3)   # some devices without
+            else:
+                net = rng.choice([0, 0, 0, 1, 1, 2]) if style < 0.7 else d // 4
+            devs.append({"id": "NPU-%04d-%d" % (i, d), "index": d, "count": 20, "devmem": 65536, "devcore": 20, "type": "Ascend910B3",
+                         "numa": d // 4, "mode": "", "health": rng.random() > 0.08, "vendor": "Ascend910B3", "network_id": net})
+        node = {"name": "asc-%04d" % i, "devices": devs}
+        if i % 3 == 0:
+            node["hami_vnpu_core"] = 1
+        nodes.append(node)
+    ops, live = [], []
+    for p in range(1600):
+        uid = "a910-%05d" % p
+        annos = {}
+        if rng.random() < 0.3:
+            annos["huawei.com/vnpu-mode"] = "hami-core"
+        if rng.random() < 0.4:
+            annos["hami.io/node-scheduler-policy"] = rng.choice(["binpack", "spread"])
+        if rng.random() < 0.3:
+            annos["hami.io/gpu-scheduler-policy"] = rng.choice(["binpack", "spread", "mutex"])
+        mem = rng.choice([0, 16384, 32768])
+        req = {"key": "Ascend910B3", "type": "Ascend910B3", "nums": rng.choice([1, 1, 2, 2, 3, 4, 6]), "memreq": mem,
+               "mempct": 100 if mem == 0 else 0, "coresreq": rng.choice([0, 5, 10])}
+        ops.append(("filter", {"uid": uid, "ns": "default", "name": uid, "annotations": annos, "containers": [[req]], "n_init": 0}))
+        live.append(uid)
+        while len(live) > 330:
+            ops.append(("delete", live.pop(rng.randrange(len(live)))))
+    cfg = {"node_policy": "binpack", "gpu_policy": "spread"}
+    ref, rsnap = parity.run_oracle(cfg, nodes, ops)
+    assert sum(1 for (k, _), r in zip(ops, ref) if k == "filter" and r.get("status") == abi.HS_FIT) > 600
+    assert sum(1 for r in ref if r.get("status") == abi.HS_NOFIT) > 10
+    got, gsnap = parity.run_engine(cfg, nodes, ops, chunk=400)
+    assert parity.compare(ops, ref, got, rsnap, gsnap) == []
