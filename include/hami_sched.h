@@ -244,7 +244,15 @@ enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
         * Annotations: the allocated key only; AWS_NEURON_IDS, NEURON_RESOURCE_TYPE, NEURON_ALLOC_TIME, NEURON_ALLOCATED and
         * aws.amazon.com/predicate-node depend on the container's resource limits (:200-243), which hs_pod does not
         * carry — the caller's own PatchAnnotations adds them from hs_filter_result.entries.                          */
-       HS_FIT_NEURON = 6 };
+       HS_FIT_NEURON = 6,
+       /* vastai (pkg/device/vastai/device.go:228-327).  Card mode: biren's gate list.  DIE mode (the node's devices say
+        * CustomInfo["DeviceStrategy"] = "die"; hs_device_info.network_id carries CustomInfo["AIC"], the card a die sits
+        * on, as a small integer that keeps the AIC strings' order): under mutex an idle die on a card with a die in use
+        * is a conflict too (:241-250,283-297); Fit collects every fitting die and picks by card — all of them when
+        * exactly `nums`, the first one when nums == 1, else cards by die count (descending; equal counts in ascending
+        * AIC, canonical rule 7), dies inside a card in walk order (:306-320,336-372); ScoreNode = largest share of one
+        * card among a container's dies, unweighted (:181-216).  A node must be all-die or all-card.                  */
+       HS_FIT_VASTAI = 7 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */

@@ -125,7 +125,7 @@ class hs_vendor_config(C.Structure):
                 ("use_type_key", C.c_char_p), ("nouse_type_key", C.c_char_p)]
 
 
-HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD, HS_FIT_METAX, HS_FIT_NEURON = 0, 1, 2, 3, 4, 5, 6
+HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD, HS_FIT_METAX, HS_FIT_NEURON, HS_FIT_VASTAI = 0, 1, 2, 3, 4, 5, 6, 7
 
 # The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
 # (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
@@ -139,7 +139,7 @@ DEFAULT_VENDORS = [
     ("AMD", HS_FIT_AMD, "amd.com/use-gpu-uuid", "amd.com/nouse-gpu-uuid", "hami.io/amd-devices-to-allocate",
      "hami.io/amd-devices-allocated", "amd.com/use-gputype", "amd.com/nouse-gputype"),
     # vastai in card mode (vastai/device.go:228-291 without DeviceStrategy "die") has biren's gate list
-    ("Vastai", HS_FIT_COUNT_ONLY, "vastaitech.com/use-gpuuuid", "vastaitech.com/nouse-gpuuuid", None, None),
+    ("Vastai", HS_FIT_VASTAI, "vastaitech.com/use-gpuuuid", "vastaitech.com/nouse-gpuuuid", None, None),
     # enflame whole-card GCU (enflame/gcu.go:31-46)
     ("GCU", HS_FIT_WHOLE_CARD, None, None, "hami.io/enflame-gcu-devices-to-allocate", "hami.io/enflame-gcu-devices-allocated"),
     # mthreads/device.go:44-58,76-80

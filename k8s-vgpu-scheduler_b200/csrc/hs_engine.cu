@@ -149,6 +149,7 @@ struct VendorInfo {
   bool neuron = false;      // AWS Neuron: core bit masks, graphSelect for several devices, per-pod awsusageinfo state (EF_NEURON)
   bool metax = false;       // metax whole GPUs: mthreads' gates without uuid lists + ScoreNode from the node's annotations (EF_METAX)
   int fit_kind = 0;         // HS_FIT_* as registered (hs_filter_simulate hands it on to the child handle)
+  bool vastai = false;      // vastai: count-only gates + die mode (EF_VASTAI)
   bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
 };
@@ -673,6 +674,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       const VendorInfo* v = vit == h->vendor_by_word.end() ? nullptr : &h->vendors[vit->second];
       e.vendor = v ? (uint16_t)v->gate : (uint16_t)HV_NONE;
       if (v && v->count_only) e.flags |= EF_COUNT_ONLY;
+      if (v && v->vastai) e.flags |= EF_VASTAI;
       if (v && v->amd) e.flags |= EF_AMD;
       if (v && (v->mthreads || v->metax)) e.flags |= EF_MTHREADS;   // metax/device.go:156-166 is mthreads' customFilterRule
       if (v && v->metax) e.flags |= EF_METAX;
@@ -695,7 +697,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
           if (!uuid_words(h, list, uuid_pool, e.nouse_off, e.nouse_cnt)) { h->err = "no-use-uuid list spans too many nodes"; return HS_ERR_UNSUPPORTED; }
       }
       keyset.insert(ktype);
-      if (v && (v->ascend910 || v->metax)) slotset.insert(ktype);   // vendors whose ScoreNode is not constant 0
+      if (v && (v->ascend910 || v->metax || v->vastai)) slotset.insert(ktype);   // vendors whose ScoreNode is not constant 0
       c.entries.push_back(e);
       c.meta.entries.push_back(EntryMeta{ktype, (int)ci, v ? v->id : -1});
       int nn = q->nums < 0 ? 0 : (q->nums > HS_D ? HS_D : q->nums);
@@ -1933,7 +1935,8 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.ascend910 = false;
       v.gate = HV_DCU;                      // iluvatar's Fit is hygon's gate list (iluvatar/device.go:267-371)
       v.fit_kind = vc.fit_kind;
-      v.count_only = vc.fit_kind == HS_FIT_COUNT_ONLY;
+      v.count_only = vc.fit_kind == HS_FIT_COUNT_ONLY || vc.fit_kind == HS_FIT_VASTAI;
+      v.vastai = vc.fit_kind == HS_FIT_VASTAI;
       v.amd = vc.fit_kind == HS_FIT_AMD;
       v.mthreads = vc.fit_kind == HS_FIT_MTHREADS;
       v.whole_card = vc.fit_kind == HS_FIT_WHOLE_CARD;

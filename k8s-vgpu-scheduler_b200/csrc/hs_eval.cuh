@@ -317,6 +317,9 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
   if (e.has_use) useMask = uuid_mask_lookup(ka.uuid_pool, e.use_off, e.use_cnt, node);
   if (e.nouse_cnt) nouseMask = uuid_mask_lookup(ka.uuid_pool, e.nouse_off, e.nouse_cnt, node);
   const bool numaAssert = isNv && (pod.flags & PF_NUMA_ASSERT);
+  // vastai die mode: isDieMode reads the FIRST device of the list (vastai/device.go:389-403); the AIC rides in NetworkID
+  const bool vastaiDie = (e.flags & EF_VASTAI) && cnt > 0 && DF_NET(w.dflags[td[0]]) != 255u;
+  if (vastaiDie) needTopology = true;       // every fitting die is collected, the choice goes by card (:306-320)
 
   for (int i = cnt - 1; i >= 0; i--) {
     const int d = td[i];
@@ -349,13 +352,19 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
     if (w.count[d] <= w.used[d]) { REASON(2); continue; }
     if (isMutex && w.used[d] > 0) { REASON(9); continue; }
     if (countOnly) {                      // biren/device.go:226-241: no memory / core gates, the pick carries no memory
+      if (vastaiDie && isMutex && DF_NET(df) != 255u) {
+        // under mutex a card is exclusive: an idle die on a card with a die in use is a conflict (vastai/device.go:241-250,283-297)
+        bool busy = false;
+        for (int t = 0; t < cnt; t++) if (w.used[td[t]] > 0 && DF_NET(w.dflags[td[t]]) == DF_NET(df)) busy = true;
+        if (busy) { REASON(9); continue; }
+      }
       if (k_nums > 0) {
-        k_nums--;
+        if (!vastaiDie) k_nums--;
         fc.tmp_dev[fc.ntmp] = d;
         fc.tmp_mem[fc.ntmp] = 0;
         fc.ntmp++;
       }
-      if (k_nums == 0) return true;
+      if (k_nums == 0 && !vastaiDie) return true;
       continue;
     }
     if (e.flags & EF_AMD) {               // amd/device.go:308-350
@@ -619,8 +628,11 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   const bool base_key[2] = {(nflags & NF_BASE_NV) != 0, (nflags & NF_BASE_MLU) != 0};
   w.mth_prev = 0;
   uint32_t metax_slots = 0;           // score slots that belong to a metax type (their accumulator is a device count)
-  for (int e = 0; e < pod.n_entries; e++)
+  uint32_t plain_slots = 0;           // … to a vastai type: ScoreNode is the plain sum, no weight (vastai/device.go:181-216)
+  for (int e = 0; e < pod.n_entries; e++) {
     if ((ent[e].flags & EF_METAX) && ent[e].score_slot >= 0) metax_slots |= 1u << ent[e].score_slot;
+    if ((ent[e].flags & EF_VASTAI) && ent[e].score_slot >= 0) plain_slots |= 1u << ent[e].score_slot;
+  }
 
   if (pod.n_init > 0) {
     int bu[HS_D], bm[HS_D], bc[HS_D];
@@ -660,7 +672,7 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   float devScore = 0.0f;
 #pragma unroll
   for (int s = 0; s < HS_SCORE_SLOTS; s++) {
-    float v = ((score_zero >> s) & 1u) ? 0.0f : __fmul_rn(score_acc[s], 10.0f);
+    float v = ((score_zero >> s) & 1u) ? 0.0f : (((plain_slots >> s) & 1u) ? score_acc[s] : __fmul_rn(score_acc[s], 10.0f));
     if ((metax_slots >> s) & 1u) {
       // 2000 - losses[n] under node policy "binpack", 2000 - scores[n] under "spread", 0 without the annotation
       const int cnt = (int)score_acc[s];

@@ -349,9 +349,11 @@ bool decode_node_json(const std::string& s, std::vector<Device>& out, std::strin
         if (v.kind != JV::Obj) { bad(type_err(v, "custominfo", "map[string]interface {}")); continue; }
         // map[string]any: numbers arrive as float64; Ascend reads CustomInfo["NetworkID"] (ascend/device.go:340-352)
         d.die_strategy = false;      // a later duplicate "custominfo" replaces the earlier map
+        d.has_aic = false; d.aic.clear();
         for (const auto& ci : v.o) {
+          if (ci.first == "AIC") { d.has_aic = ci.second.kind == JV::Str; d.aic = d.has_aic ? ci.second.s : std::string(); }
           if (ci.first == "NetworkID" && ci.second.kind == JV::Num) d.network_id = (int32_t)std::strtod(ci.second.s.c_str(), nullptr);
-          // vastai's isDieMode (vastai/device.go:389-403): per-die state (AIC ids) that the inventory record does not carry
+          // vastai's isDieMode (vastai/device.go:389-403)
           if (ci.first == "DeviceStrategy") d.die_strategy = ci.second.kind == JV::Str && ci.second.s == "die";
         }
       }

@@ -14,7 +14,9 @@ struct Device {            // device.DeviceInfo, the fields the scheduler path r
   bool health = false;
   int32_t network_id = -1; // CustomInfo["NetworkID"] (Ascend), -1 = absent
   bool has_mig_profiles = false;
-  bool die_strategy = false; // CustomInfo["DeviceStrategy"] == "die" (vastai die mode): decoded, but refused at registration
+  bool die_strategy = false; // CustomInfo["DeviceStrategy"] == "die" (vastai die mode)
+  bool has_aic = false;      // CustomInfo["AIC"] is a string: the card the die sits on (vastai/device.go:374-387)
+  std::string aic;
 };
 
 struct PodEntry {          // one ContainerDevice, flattened with its PodDevices key and container index

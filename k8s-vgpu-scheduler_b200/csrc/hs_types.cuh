@@ -59,6 +59,7 @@ enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
 #define EF_WHOLE_CARD 64u  // enflame GCU's Fit (enflame/gcu.go:144-183): health, type, "in use at all" = conflict; no uuid lists, no slot count
 #define EF_MTHREADS 32u    // mthreads' Fit (mthreads/device.go:289-405): template gates + customFilterRule (one card per pod)
 #define EF_AMD 16u         // amd's Fit (amd/device.go:279-371): whole-card memory by default, cores as a share of the card
+#define EF_VASTAI 512u     // vastai: EF_COUNT_ONLY gates; on a node of dies (NetworkID = AIC) card exclusivity under mutex, pick by card, ScoreNode
 #define EF_COUNT_ONLY 8u   // biren's Fit (biren/device.go:190-248): gates end after mutex; the pick has Usedmem 0, Usedcores = Coresreq
 
 struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 64 B

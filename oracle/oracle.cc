@@ -367,7 +367,7 @@ namespace {
 // WHOLE_CARD: enflame GCU (enflame/gcu.go:144-183) — health, type, "in use at all" = conflict; no uuid lists, no slot count
 // METAX: the whole-GPU "Metax-GPU" device (metax/device.go:223-334) — the template gates with no uuid lists
 //   (checkUUID is constant true, :124-126) plus the same customFilterRule as mthreads (:156-166)
-enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY, AMD, MTHREADS, WHOLE_CARD, METAX };
+enum class Vendor { NVIDIA, DCU, MLU, ASCEND, PLAIN, COUNT_ONLY, AMD, MTHREADS, WHOLE_CARD, METAX, VASTAI };
 
 struct FitGates {
   Vendor vendor;
@@ -540,6 +540,11 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
     }
   }
   const bool is910CMulti = g.vendor == Vendor::ASCEND && k.Type == "Ascend910C" && originReq > 1;
+  // vastai: isDieMode looks at the FIRST device of the (sorted) list (vastai/device.go:389-403); occupied cards under mutex (:241-250)
+  const bool vastaiDie = g.vendor == Vendor::VASTAI && !devices.empty() && devices[0]->HasNetworkID;
+  std::set<int> vastaiBusyAIC;
+  if (vastaiDie && isMutex)
+    for (auto d : devices) if (d->Used > 0 && d->HasNetworkID) vastaiBusyAIC.insert(d->NetworkID);
 
   for (int i = (int)devices.size() - 1; i >= 0; i--) {
     DeviceUsage* dev = devices[i];
@@ -571,6 +576,7 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
         case Vendor::METAX:        // metax/device.go:117-122
         case Vendor::PLAIN:        // iluvatar/device.go:190-195
         case Vendor::COUNT_ONLY:   // biren/device.go:130-135
+        case Vendor::VASTAI:       // vastai/device.go:126-131
           found = true;
           break;
       }
@@ -598,6 +604,21 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
     int32_t memreq = 0;
     if (dev->Count <= dev->Used) { reason["CardTimeSlicingExhausted"]++; continue; }
     if (isMutex && dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+    if (g.vendor == Vendor::VASTAI) {
+      // vastai/device.go:228-327.  Card mode is biren's gate list; in DIE mode (the first device of the list says
+      // DeviceStrategy "die": CustomInfo["AIC"] rides in NetworkID) a card is made of several dies: under mutex an idle
+      // die on a card with a die in use is a conflict too, every fitting die is collected, and the choice goes by card
+      if (isMutex && vastaiDie && dev->HasNetworkID && vastaiBusyAIC.count(dev->NetworkID)) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+      if (k.Nums > 0) {
+        if (!vastaiDie) k.Nums--;
+        ContainerDevice cd;
+        cd.Idx = (int)dev->Index; cd.UUID = dev->ID; cd.Type = k.Type; cd.Usedmem = 0; cd.Usedcores = k.Coresreq;
+        cd.HasNetworkID = dev->HasNetworkID; cd.NetworkID = dev->NetworkID;      // CustomInfo: dev.CustomInfo
+        tmpDevs.push_back(cd);
+      }
+      if (k.Nums == 0 && !vastaiDie) { FitResult r; r.fit = true; r.devs = tmpDevs; return r; }
+      continue;
+    }
     if (g.vendor == Vendor::COUNT_ONLY) {   // biren/device.go:226-241: no memory / core gates, the pick carries no memory
       if (k.Nums > 0) {
         k.Nums--;
@@ -680,6 +701,15 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
     }
   }
 
+  if (vastaiDie) {    // vastai/device.go:306-320; computeBestCombination :336-372 (cards with equal die counts: ascending AIC, canonical rule 7)
+    if ((int)tmpDevs.size() == (int)originReq) { FitResult r; r.fit = true; r.devs = tmpDevs; return r; }
+    if ((int)tmpDevs.size() > (int)originReq) {
+      FitResult r; r.fit = true;
+      if (originReq == 1) r.devs = ContainerDevices{tmpDevs[0]};
+      else r.devs = ascendBestCombination((int)originReq, tmpDevs);
+      return r;
+    }
+  }
   if (is910CMulti) {  // ascend/device.go:582-593
     ContainerDevices combination = ascendBestCombination910C((int)originReq, tmpDevs);
     if ((int)combination.size() != (int)originReq) {
@@ -897,8 +927,9 @@ class PlainDevices : public Devices {
   FitResult Fit(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
                 const NodeInfo* nodeInfo, const std::string& def, const PodDevices* allocated,
                 const QuotaManager* quota) const override {
-    static const Vendor kinds[] = {Vendor::PLAIN, Vendor::COUNT_ONLY, Vendor::AMD, Vendor::MTHREADS, Vendor::WHOLE_CARD, Vendor::METAX};
-    FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 5 ? v_.FitKind : 0],
+    static const Vendor kinds[] = {Vendor::PLAIN, Vendor::COUNT_ONLY, Vendor::AMD, Vendor::MTHREADS, Vendor::WHOLE_CARD, Vendor::METAX,
+                                   Vendor::PLAIN /* 6 = Neuron, below */, Vendor::VASTAI};
+    FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 7 ? v_.FitKind : 0],
                v_.CommonWord,
                v_.UseType, v_.NoUseType, v_.UseUUID, v_.NoUseUUID};
     if (v_.FitKind == 6) return fitNeuron(g, devices, request, pod, def);
@@ -913,6 +944,22 @@ class PlainDevices : public Devices {
   }
   // metax/device.go:185-214: 2000 minus the node's topology loss (binpack) / score (spread) for this many devices
   float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo) const override {
+    if (v_.FitKind == 7) {            // vastai/device.go:181-216: largest share of one card among a container's dies, unweighted
+      float score = 0;
+      for (auto& containerDevices : podDevices) {
+        if (containerDevices.empty()) continue;
+        std::map<int, int> cntMap;
+        for (auto& d : containerDevices) {
+          if (!d.HasNetworkID) return 0;          // no CustomInfo / not a die / no AIC
+          cntMap[d.NetworkID]++;
+        }
+        int maxCnt = 0, totalCnt = 0;
+        for (auto& kv : cntMap) { if (kv.second > maxCnt) maxCnt = kv.second; totalCnt += kv.second; }
+        if (totalCnt == 0) continue;
+        score = score + (float)maxCnt / (float)totalCnt;
+      }
+      return score;
+    }
     if (v_.FitKind != 5) return 0;
     int sum = 0;
     for (auto& ctr : podDevices) sum += (int)ctr.size();

@@ -79,6 +79,8 @@ def dev_from_go(d, score=0.0):
     ci = d.get("CustomInfo")
     if isinstance(ci, dict) and "NetworkID" in ci:
         net = int(ci["NetworkID"])
+    if isinstance(ci, dict) and ci.get("DeviceStrategy") == "die" and "AIC" in ci:   # vastai die: the card id (digit strings in the fixtures) rides in NetworkID
+        net = int(ci["AIC"])
     if isinstance(ci, dict) and "AWSNodeType" in ci:      # carried as 1 (contains "inf"/"Inf": ring) / 0 (awsneuron/device.go:414)
         net = 1 if ("inf" in ci["AWSNodeType"] or "Inf" in ci["AWSNodeType"]) else 0
     return oracle_dev(abi._b(d.get("ID", "")), int(d.get("Index", 0)), int(d.get("Used", 0)), int(d.get("Count", 0)),

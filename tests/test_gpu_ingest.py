@@ -98,11 +98,16 @@ def test_register_skips_bad_vendors_and_removes_empty_nodes():
     assert e.node_count() == 0
     assert e.node_register("n2", [("NVIDIA", abi.HS_REG_JSON, "not-valid-json", None)]) == 0
     assert e.node_count() == 0
-    # vastai dies (custominfo.DeviceStrategy = "die") carry per-die state the inventory record has no room for: skipped loudly
-    die = '[{"id":"va-0","count":1,"type":"Vastai","health":true,"custominfo":{"DeviceStrategy":"die","AIC":"1"}}]'
+    # vastai dies (custominfo.DeviceStrategy = "die"): the card a die sits on (AIC) is registered with it; a node that mixes
+    # dies and whole cards is skipped loudly
+    die = '[{"id":"va-0","count":1,"type":"Vastai","health":true,"custominfo":{"DeviceStrategy":"die","AIC":"1"}},' \
+          '{"id":"va-1","count":1,"type":"Vastai","health":true,"custominfo":{"DeviceStrategy":"die","AIC":"0"}}]'
+    mixed = '[{"id":"va-0","count":1,"type":"Vastai","health":true,"custominfo":{"DeviceStrategy":"die","AIC":"1"}},' \
+            '{"id":"va-1","count":1,"type":"Vastai","health":true}]'
     card = '[{"id":"va-0","count":1,"type":"Vastai","health":true,"custominfo":{"DeviceStrategy":"card"}}]'
-    assert e.node_register("n3", [("Vastai", abi.HS_REG_JSON, die, None), ("NVIDIA", abi.HS_REG_JSON, good, None)]) == 1
-    assert "die" in e.error() and e.node_count() == 1
+    assert e.node_register("n3", [("Vastai", abi.HS_REG_JSON, die, None), ("NVIDIA", abi.HS_REG_JSON, good, None)]) == 3
+    assert e.node_register("n5", [("Vastai", abi.HS_REG_JSON, mixed, None), ("NVIDIA", abi.HS_REG_JSON, good.replace("GPU-a", "GPU-b"), None)]) == 1
+    assert "die" in e.error() and e.node_count() == 2
     assert e.node_register("n4", [("Vastai", abi.HS_REG_JSON, card, None)]) == 1
     e.close()
 

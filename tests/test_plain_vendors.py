@@ -72,10 +72,8 @@ def test_mthreads_fit(orc, case):
 @pytest.mark.parametrize("case", load("vastai_fit"), ids=[c["name"] for c in load("vastai_fit")])
 def test_vastai_fit_card_mode(orc, case):
     # vastai/device_test.go:542-901.  Card mode (no CustomInfo DeviceStrategy "die") has biren's gate list; the two die-mode
-    # cases need the per-die AIC id of CustomInfo, which the inventory record does not carry.
-    if any("die" in json.dumps(d) for d in case["devices"]):
-        pytest.skip("vastai die mode (AIC exclusivity, best-combination search) is not built")
-    annos = case["annos"] if isinstance(case["annos"], dict) else {}
+    # cases exercise the AIC exclusivity under mutex (the card a die sits on rides in NetworkID).
+    annos = case.get("annos") or {}
     fit, got, reason = run_fit(orc, "Vastai", case["devices"], case["request"], annos)
     assert fit == case["wantFit"]
     if fit:
@@ -155,6 +153,26 @@ def test_amd_allocation_keeps_the_product_type():
     assert r["devices"].get("AMD_Instinct_MI300X_VF") == [[]]        # base-type padding (score.go:278-282), no devices under it
 
 
+def test_vastai_best_combination_by_card(orc):
+    # vastai/device_test.go:954-1060 (TestComputeBestCombination) through Fit on a node of idle dies: all dies fit, so the
+    # choice is computeBestCombination's — cards by die count, dies inside a card in walk order
+    def dies(spec):
+        return [{"ID": "dev%d" % i, "Index": i, "Count": 1, "Used": 0, "Type": "Vastai", "Health": True,
+                 "CustomInfo": {"AIC": aic, "DeviceStrategy": "die"}} for i, aic in spec]
+    # walk order is the list from the END: ids are numbered so that the expected picks read like the reference's table
+    fit, got, _ = run_fit(orc, "Vastai", dies([(3, "1"), (2, "1"), (1, "1")]), {"Nums": 2, "Type": "Vastai"}, {})
+    assert fit and [g[0] for g in got] == ["dev1", "dev2"]
+    six = [(6, "3"), (5, "2"), (4, "2"), (3, "1"), (2, "1"), (1, "1")]
+    fit, got, _ = run_fit(orc, "Vastai", dies(six), {"Nums": 3, "Type": "Vastai"}, {})
+    assert fit and [g[0] for g in got] == ["dev1", "dev2", "dev3"]
+    fit, got, _ = run_fit(orc, "Vastai", dies(six), {"Nums": 4, "Type": "Vastai"}, {})
+    assert fit and [g[0] for g in got] == ["dev1", "dev2", "dev3", "dev4"]
+    fit, got, reason = run_fit(orc, "Vastai", dies([(3, "2"), (2, "1"), (1, "1")]), {"Nums": 5, "Type": "Vastai"}, {})
+    assert not fit and reason == "3/3 AllocatedCardsInsufficientRequest"
+    fit, got, _ = run_fit(orc, "Vastai", dies(six), {"Nums": 1, "Type": "Vastai"}, {})
+    assert fit and [g[0] for g in got] == ["dev1"]                                  # nums == 1: the first die of the walk
+
+
 # ---- GPU parity on a generated cluster ---------------------------------------------------------------------
 def _cluster(n_nodes, n_pods, seed=11):
     rng = random.Random(seed)
@@ -173,6 +191,8 @@ def _cluster(n_nodes, n_pods, seed=11):
             elif kind in ("Biren", "Vastai"):
                 devs.append({"id": "%s-%03d-%d" % (kind[:2].upper(), i, d), "index": d, "count": rng.choice([1, 1, 2]), "devmem": 0,
                              "devcore": 0, "type": kind, "numa": 0, "mode": "", "health": rng.random() > 0.05, "vendor": kind})
+                if kind == "Vastai" and (i // 8) % 2 == 0:      # every other vastai node is a node of DIES: d // 2 or d // 3 is the card
+                    devs[-1]["network_id"] = d // (2 + (i // 16) % 2)
             elif kind == "Mthreads":
                 devs.append({"id": "pv-%03d-mthreads-%d" % (i, d), "index": d, "count": 100, "devmem": 49152, "devcore": 16,
                              "type": "Mthreads", "numa": 0, "mode": "", "health": True, "vendor": "Mthreads"})
