@@ -404,30 +404,35 @@ def b2_baseline(cfg, nodes, pods0, probe_ops, sample_ops, e2, oa, threads):
             return None
         n_probe = len(probe_ops)
         sec_all, out = b2.run(stream)           # the whole stream once: the decisions that are checked
-        b2s = oa.B2(nodes, threads)        # timing: the sample alone, from the state after the probe
-        for uid, node, rows in pods0:
-            for uuid, slots, mem, cores in rows:
-                b2s.usage_add(uuid, slots, mem, cores)
-        b2s.run(stream[:n_probe])
-        rebased = []
-        for op in stream[n_probe:]:
-            if op.kind == 1:
-                if op.rel_op < n_probe:          # releases a probe-phase decision: hand it over as an explicit (node, rows) release
-                    src = out[op.rel_op]
-                    q = oa.b2_op()
-                    q.kind, q.rel_node = 2, src.node
-                    for k in range(src.n_picks):
-                        d = src.picks[k]
-                        q.rel_rows[d][0] += 1; q.rel_rows[d][1] += src.memreq[k]; q.rel_rows[d][2] += src.cores
-                    rebased.append(q)
-                    continue
-                q = oa.b2_op()
-                q.kind, q.rel_op = 1, op.rel_op - n_probe
-                rebased.append(q)
-            else:
-                rebased.append(op)
-        sec, _ = b2s.run(rebased)
-        b2s.close()
+        rebased = None
+        timings = {}
+        for T in sorted({1, threads}):         # timing: the sample alone, from the state after the probe, at 1 thread and at all cores
+            b2s = oa.B2(nodes, T)
+            for uid, node, rows in pods0:
+                for uuid, slots, mem, cores in rows:
+                    b2s.usage_add(uuid, slots, mem, cores)
+            b2s.run(stream[:n_probe])
+            if rebased is None:
+                rebased = []
+                for op in stream[n_probe:]:
+                    if op.kind == 1 and op.rel_op < n_probe:      # releases a probe-phase decision: an explicit (node, rows) release
+                        src = out[op.rel_op]
+                        q = oa.b2_op()
+                        q.kind, q.rel_node = 2, src.node
+                        for k in range(src.n_picks):
+                            d = src.picks[k]
+                            q.rel_rows[d][0] += 1; q.rel_rows[d][1] += src.memreq[k]; q.rel_rows[d][2] += src.cores
+                        rebased.append(q)
+                    elif op.kind == 1:
+                        q = oa.b2_op()
+                        q.kind, q.rel_op = 1, op.rel_op - n_probe
+                        rebased.append(q)
+                    else:
+                        rebased.append(op)
+            timings[T], _ = b2s.run(rebased)
+            b2s.close()
+        best_T = min(timings, key=timings.get)
+        sec = timings[best_T]
         # decisions of the sample against the engine's
         slot = b2.dev_slot
         bad, nfil = 0, 0
@@ -445,8 +450,9 @@ def b2_baseline(cfg, nodes, pods0, probe_ops, sample_ops, e2, oa, threads):
                     struct.pack("f", d.score) == struct.pack("f", g["score"]) and
                     [slot[r[0]][1] for r in rows] == [d.picks[k] for k in range(d.n_picks)])
             bad += not same
-        return {"value": round(nfil / sec, 1), "unit": UNIT, "cores": threads, "kind": "port (lean: SoA, no strings, persistent thread pool)",
-                "seconds": round(sec, 3), "filters": nfil, "mismatches_vs_engine": int(bad)}
+        return {"value": round(nfil / sec, 1), "unit": UNIT, "cores": best_T, "kind": "port (lean: SoA, no strings, persistent thread pool)",
+                "seconds": round(sec, 3), "filters": nfil, "mismatches_vs_engine": int(bad),
+                "by_threads": {str(T): round(nfil / t, 1) for T, t in sorted(timings.items())}}
     finally:
         b2.close()
 

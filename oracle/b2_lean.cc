@@ -12,6 +12,8 @@
 // for those; B2 is only ever timed next to it and its decisions are compared with the oracle's on the timed sample.
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <mutex>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -64,9 +66,13 @@ struct B2 {
   int threads = 1;
   // persistent pool
   std::vector<std::thread> pool;
-  std::atomic<int> phase{0};
-  std::atomic<int> arrived{0};
-  std::atomic<bool> quit{false};
+  // one barrier per decision: the workers sleep on a condition variable between decisions (a spinning pool burns the
+  // container's CPU quota and gets throttled for it, which is far slower than the wake-up)
+  std::mutex mu;
+  std::condition_variable cv_go, cv_done;
+  int phase = 0;
+  int arrived = 0;
+  bool quit = false;
   const b2_op* cur = nullptr;
   std::vector<uint64_t> part_key;
   std::vector<b2_decision> out;
@@ -238,8 +244,12 @@ void worker(B2* h, int tid) {
   const size_t n = h->nodes.size();
   const size_t lo = n * (size_t)tid / (size_t)h->threads, hi = n * (size_t)(tid + 1) / (size_t)h->threads;
   for (;;) {
-    while (h->phase.load(std::memory_order_acquire) == seen) { if (h->quit.load(std::memory_order_relaxed)) return; }
-    seen++;
+    {
+      std::unique_lock<std::mutex> lk(h->mu);
+      h->cv_go.wait(lk, [&] { return h->phase != seen || h->quit; });
+      if (h->quit) return;
+      seen = h->phase;
+    }
     const b2_op& p = *h->cur;
     uint64_t best = 0;
     for (size_t i = lo; i < hi; i++) {
@@ -247,7 +257,11 @@ void worker(B2* h, int tid) {
       if (verdict(nd, p)) { const uint64_t k = make_key(nd.score, p.node_spread, (uint32_t)i); if (k > best) best = k; }
     }
     h->part_key[(size_t)tid * 8] = best;          // one cache line per thread
-    h->arrived.fetch_add(1, std::memory_order_release);
+    {
+      std::lock_guard<std::mutex> lk(h->mu);
+      h->arrived++;
+    }
+    h->cv_done.notify_one();
   }
 }
 
@@ -265,7 +279,8 @@ void* b2_create(int32_t n_nodes, int32_t threads) {
 }
 void b2_destroy(void* hv) {
   B2* h = (B2*)hv;
-  h->quit.store(true);
+  { std::lock_guard<std::mutex> lk(h->mu); h->quit = true; }
+  h->cv_go.notify_all();
   for (auto& t : h->pool) t.join();
   delete h;
 }
@@ -312,14 +327,19 @@ double b2_run(void* hv, const b2_op* ops, int32_t n_ops, b2_decision* out) {
       continue;
     }
     h->cur = &p;
-    h->arrived.store(0, std::memory_order_relaxed);
-    h->phase.fetch_add(1, std::memory_order_release);
+    if (h->threads > 1) {
+      { std::lock_guard<std::mutex> lk(h->mu); h->arrived = 0; h->phase++; }
+      h->cv_go.notify_all();
+    }
     uint64_t best = 0;
     for (size_t k = 0; k < hi0; k++) {                   // the calling thread is worker 0
       const B2Node& nd = h->nodes[k];
       if (verdict(nd, p)) { const uint64_t key = make_key(nd.score, p.node_spread, (uint32_t)k); if (key > best) best = key; }
     }
-    while (h->arrived.load(std::memory_order_acquire) < h->threads - 1) {}
+    if (h->threads > 1) {
+      std::unique_lock<std::mutex> lk(h->mu);
+      h->cv_done.wait(lk, [&] { return h->arrived >= h->threads - 1; });
+    }
     for (int t = 1; t < h->threads; t++) if (h->part_key[(size_t)t * 8] > best) best = h->part_key[(size_t)t * 8];
     if (!best) continue;
     const uint32_t pos = (uint32_t)(best & 0xffffffffu) - 1u;
