@@ -238,6 +238,58 @@ __device__ __forceinline__ unsigned long long slot_wait(OpSync* slot, unsigned l
   return *s_win;
 }
 
+// The multi-GPU barrier in the same two halves.  xgpu_arrive: every CTA folds its key into the local slot and
+// signals; the rank's leader (CTA 0, lane 0 of warp 0) then waits for this GPU's CTAs and posts the shard's key to
+// every rank's mailbox.  xgpu_wait: warp 0 of every CTA polls this GPU's own mailbox row.  Between the two the
+// groups that fit run their full evaluation, so it overlaps the NVLink round trip instead of preceding it (only
+// the leader's own warp 0 does that work after its post, not beside it).
+__device__ __forceinline__ void xgpu_arrive(const KernelArgs& ka, OpSync* slot, uint32_t b,
+                                            unsigned long long warp_key, unsigned long long* s_red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  if (lane == 0) s_red[warp] = warp_key;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned long long v = lane < nwarps ? s_red[lane] : 0ull;
+    v = warp_max_u64(v);
+    if (lane == 0) {
+      if (v) atomicMax(&slot->best, v);
+      asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(&slot->arrived) : "memory");
+      if (blockIdx.x == 0) {
+        const unsigned long long epoch = (unsigned long long)((ka.epoch_base + b + 1u) & 255u);
+        const uint32_t row = (ka.epoch_base + b) & 3u;
+        const unsigned long long best = slot_poll(slot);
+        const unsigned long long mine = (best & ~255ull) | epoch;
+        for (int p = 1; p <= ka.world; p++) {     // peers first, own mailbox last
+          const int q = (ka.rank + p) % ka.world;
+          asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(ka.mbox_peer[q] + row * 8 + ka.rank), "l"(mine) : "memory");
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
+__device__ __forceinline__ unsigned long long xgpu_wait(const KernelArgs& ka, uint32_t b, unsigned long long* s_win) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (warp == 0) {
+    const unsigned long long epoch = (unsigned long long)((ka.epoch_base + b + 1u) & 255u);
+    const uint32_t row = (ka.epoch_base + b) & 3u;
+    const unsigned long long* my_box = ka.mbox_peer[ka.rank] + row * 8;
+    unsigned long long w = epoch;
+    uint32_t spins = 0;
+    bool ok;
+    do {
+      if (lane < ka.world) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(my_box + lane) : "memory");
+      ok = __all_sync(0xffffffffu, (w & 255ull) == epoch);
+    } while (!ok && ++spins < XGPU_SPIN_LIMIT);
+    if (!ok) { if (lane == 0) ka.counters[6] = 1u; w = 0; }
+    w = lane < ka.world ? (w & ~255ull) : 0ull;
+    w = warp_max_u64(w);
+    if (lane == 0) *s_win = w;
+  }
+  __syncthreads();
+  return *s_win;
+}
+
 // ---- request staging: op records (160 B) are prefetched with cp.async into a ring of HS_PF shared-memory
 // buffers, HS_PF-1 ops ahead: a RELEASE op is only a few hundred cycles long, shorter than the L2 latency of the
 // next record, so a distance of one op stalled every short op on its successor's fetch.  Every op position issues
@@ -426,9 +478,10 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
     // streaming mode only: in resident mode the full evaluation runs in parallel everywhere, so the winner can
     // commit straight after the barrier (measured: deferring it to the winner lengthens the critical path)
     // Without numa-bind the VERDICT needs no score/sort (fast_fit_lite).  Streaming mode: the winner's warp runs the
-    // full evaluation afterwards.  Resident mode on one GPU: every group that fits runs it while the barrier's
-    // arrivals are in flight (`deferred`), so the winner still commits straight after the barrier.
-    const bool lite = fast && !hs_verdict_needs_order(pod) && (!resident || ka.world <= 1);
+    // full evaluation afterwards.  Resident mode: every group that fits runs it while the barrier's
+    // arrivals (and, across GPUs, the mailbox round trip) are in flight (`deferred`), so the winner still commits
+    // straight after the barrier.
+    const bool lite = fast && !hs_verdict_needs_order(pod);
     const bool deferred = lite && resident;
     const DevEntry* ent = &pod.e0;
     if (pod.n_entries > 1) {     // general path with several entries: fetch them from the pool
@@ -546,6 +599,10 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
         ka.trace[(size_t)(r - ka.op_begin) * ka.trace_stride + ka.trace_stride - 1] = t_;
       }
+    } else if (deferred) {
+      xgpu_arrive(ka, ka.sync + r, barriers, bk, s_red);
+      if (__any_sync(FULL, my_key != 0ull)) fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
+      win = xgpu_wait(ka, barriers, &s_win);
     } else {
       win = slot_argbest(ka, ka.sync + r, barriers, bk, s_red, &s_win);
     }
