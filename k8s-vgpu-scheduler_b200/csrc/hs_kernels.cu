@@ -232,6 +232,16 @@ __device__ __forceinline__ void slot_arrive(OpSync* slot, unsigned long long war
     }
   }
 }
+// max of the warp keys slot_arrive left in s_red (every lane reads all of them: broadcast loads, no shuffles)
+__device__ __forceinline__ unsigned long long cta_best(const unsigned long long* s_red) {
+  const int nwarps = blockDim.x >> 5;
+  unsigned long long m = 0;
+  for (int w = 0; w < nwarps; w++) {
+    const unsigned long long v = s_red[w];
+    m = v > m ? v : m;
+  }
+  return m;
+}
 __device__ __forceinline__ unsigned long long slot_wait(OpSync* slot, unsigned long long* s_win) {
   if (threadIdx.x == 0) *s_win = slot_poll(slot);
   __syncthreads();
@@ -589,7 +599,9 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
         ka.trace[(size_t)(r - ka.op_begin) * ka.trace_stride + blockIdx.x] = t_;
       }
-      if (deferred && __any_sync(FULL, my_key != 0ull))     // warp-uniform: fast_fit is a whole-warp collective
+      // Only the warp that holds the CTA's best key can hold the winner: the others skip the full evaluation and
+      // leave the issue slots to it (s_red holds every warp's key since slot_arrive's __syncthreads).
+      if (deferred && bk != 0ull && bk == cta_best(s_red))  // warp-uniform: fast_fit is a whole-warp collective
         fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
       // (choosing the devices here too, in every group that fits, was measured 8 % SLOWER than leaving fast_pick to
       // the one winner: 5 000 groups pay for it, one benefits)
@@ -601,7 +613,7 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
       }
     } else if (deferred) {
       xgpu_arrive(ka, ka.sync + r, barriers, bk, s_red);
-      if (__any_sync(FULL, my_key != 0ull)) fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
+      if (bk != 0ull && bk == cta_best(s_red)) fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
       win = xgpu_wait(ka, barriers, &s_win);
     } else {
       win = slot_argbest(ka, ka.sync + r, barriers, bk, s_red, &s_win);
