@@ -42,7 +42,7 @@ enum {
   HS_FIT_REMOTE = 3,     /* sharded mode: a node on ANOTHER rank's shard was chosen; node_index = global position */
   HS_ERR_INVALID = -1,   /* malformed argument / unsupported shape        */
   HS_ERR_CUDA = -2,      /* CUDA runtime failure; see hs_last_error       */
-  HS_ERR_UNSUPPORTED = -3,/* feature outside the built scope (dynamic MIG, …) */
+  HS_ERR_UNSUPPORTED = -3,/* feature outside the built scope */
   HS_ERR_WEIGHTS = -4,   /* invalid hami.io/device-scoring-weights: whole Filter errors (score.go:361-364) */
   HS_ERR_NOTFOUND = -5
 };
@@ -69,6 +69,22 @@ enum {
 
 /* ---- inventory --------------------------------------------------------- */
 
+/* Dynamic MIG: device.MigPlacement / device.MigProfile (pkg/device/devices.go:50-53,79-90) as the
+ * device plugin reports them for a GPU in MIG mode.  A placement with size 0 is refused (the reference's Fit
+ * would visit such a GPU forever, nvidia/device.go:846-848); start + size <= 8, at most 16 profiles per GPU,
+ * 8 placements per profile and 15 distinct geometries (profile lists) per handle.                              */
+typedef struct hs_mig_placement {
+  uint32_t start, size;
+} hs_mig_placement;
+typedef struct hs_mig_profile {
+  const char*             name;        /* "1g.10gb", …                                  */
+  int32_t                 memory_mb;
+  int32_t                 core;
+  uint32_t                slice_count;
+  const hs_mig_placement* placements;
+  uint32_t                n_placements;
+} hs_mig_profile;
+
 /* device.DeviceInfo (pkg/device/devices.go:127-144) as the register path hands
  * it to nodeManager.addNode (pkg/scheduler/nodes.go:76).                    */
 typedef struct hs_device_info {
@@ -83,6 +99,8 @@ typedef struct hs_device_info {
   uint8_t     health;
   const char* vendor;    /* DevicesMap key == CommonWord(): "NVIDIA", "DCU", "MLU", "Ascend910B3", … */
   int32_t     network_id;/* CustomInfo["NetworkID"] (Ascend), -1 = absent */
+  const hs_mig_profile* mig_profiles;   /* DeviceInfo.MIGProfiles (devices.go:141); read for mode "mig" only */
+  uint32_t    n_mig_profiles;
 } hs_device_info;
 
 /* device.NodeInfo (pkg/device/devices.go:170-174) plus the node annotations the
@@ -153,6 +171,10 @@ typedef struct hs_alloc_entry {
   int32_t     idx;
   int32_t     usedmem;
   int32_t     usedcores;
+  /* CustomInfo["migProfile"] / ["migPlacement"] of a pick on a GPU in MIG mode (nvidia/device.go:653-657): the
+   * reservation AddResourceUsage made; usedmem / usedcores are then the profile's.  NULL = not a MIG pick.       */
+  const char* mig_profile;
+  uint32_t    mig_start, mig_size;
 } hs_alloc_entry;
 
 /* Per failed node: reason string exactly as common.GenReason renders it
@@ -481,6 +503,23 @@ int32_t hs_node_register(hs_handle* h, const char* node, const hs_vendor_registr
  * hami.io/vgpu-node; it must be registered (HS_ERR_NOTFOUND otherwise: ingest nodes first).                  */
 int32_t hs_pod_ingest(hs_handle* h, const char* pod_uid, const char* ns, const char* node, const hs_kv* annotations,
                       uint32_t n_annotations, uint32_t n_init);
+
+/* Dynamic MIG, the informer side (scheduler.go:757-842): the decoded hami.io/vgpu-mig-allocations annotation of a
+ * pod the cache holds (nvidia.DecodeMigAllocations, nvidia/mig_allocations.go:78-112), in annotation order.  Filter
+ * itself caches the pod WITHOUT it (args.Pod is not patched in place, scheduler.go:1135-1139), so every GPU in MIG
+ * mode it picked fails closed ("MIG Pod lacks a matching profile/placement reservation") until the informer delivers
+ * the patched pod: hs_pod_ingest decodes the annotation itself, hs_pod_set_mig is the same step for callers that
+ * feed the cache through hs_usage_apply.  n = 0 clears the pod's reservations.                                      */
+typedef struct hs_mig_reservation {
+  const char* gpu_uuid;
+  const char* profile;
+  uint32_t    start, size;
+} hs_mig_reservation;
+int32_t hs_pod_set_mig(hs_handle* h, const char* pod_uid, const hs_mig_reservation* res, uint32_t n);
+/* What getNodesUsage would hand Fit for one node's MIG state: per device the occupied-slice mask (bit s = slice s
+ * is covered by a reservation in use) and whether the device is healthy after the fail-closed rules.  Rows in the
+ * node's device order; returns the number of devices.                                                           */
+int32_t hs_snapshot_node_mig(hs_handle* h, const char* node, uint32_t* occupied, uint8_t* health, uint32_t cap);
 
 /* ---- namespace quota: device.QuotaManager, pkg/device/quota.go ------------------------------
  * The NVIDIA and MLU Fit refuse a device when the pod's collapsed total would push the namespace past a configured

@@ -18,10 +18,50 @@ REASONS = [
 ]
 
 
+class hs_mig_placement(C.Structure):
+    _fields_ = [("start", C.c_uint32), ("size", C.c_uint32)]
+
+
+class hs_mig_profile(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("memory_mb", C.c_int32), ("core", C.c_int32), ("slice_count", C.c_uint32),
+                ("placements", C.POINTER(hs_mig_placement)), ("n_placements", C.c_uint32)]
+
+
+class hs_mig_reservation(C.Structure):
+    _fields_ = [("gpu_uuid", C.c_char_p), ("profile", C.c_char_p), ("start", C.c_uint32), ("size", C.c_uint32)]
+
+
 class hs_device_info(C.Structure):
     _fields_ = [("id", C.c_char_p), ("index", C.c_uint32), ("count", C.c_int32), ("devmem", C.c_int32),
                 ("devcore", C.c_int32), ("type", C.c_char_p), ("numa", C.c_int32), ("mode", C.c_char_p),
-                ("health", C.c_uint8), ("vendor", C.c_char_p), ("network_id", C.c_int32)]
+                ("health", C.c_uint8), ("vendor", C.c_char_p), ("network_id", C.c_int32),
+                ("mig_profiles", C.POINTER(hs_mig_profile)), ("n_mig_profiles", C.c_uint32)]
+
+
+def build_mig_profiles(profiles, keep):
+    """[{name, memory_mb, core, slice_count, placements: [(start, size)]}] -> (hs_mig_profile array, n)"""
+    if not profiles:
+        return None, 0
+    arr = (hs_mig_profile * len(profiles))()
+    for i, p in enumerate(profiles):
+        pl = p.get("placements") or []
+        parr = (hs_mig_placement * max(1, len(pl)))()
+        for j, (st, sz) in enumerate(pl):
+            parr[j] = hs_mig_placement(st, sz)
+        keep.append(parr)
+        arr[i] = hs_mig_profile(_b(p["name"]), p.get("memory_mb", 0), p.get("core", 0), p.get("slice_count", 0),
+                                parr, len(pl))
+    keep.append(arr)
+    return arr, len(profiles)
+
+
+def build_mig_reservations(res, keep):
+    """[(gpu_uuid, profile, start, size)] -> (hs_mig_reservation array, n)"""
+    arr = (hs_mig_reservation * max(1, len(res)))()
+    for i, (u, p, st, sz) in enumerate(res):
+        arr[i] = hs_mig_reservation(_b(u), _b(p), st, sz)
+    keep.append(arr)
+    return arr, len(res)
 
 
 class hs_node_info(C.Structure):
@@ -70,7 +110,8 @@ class hs_pod(C.Structure):
 
 class hs_alloc_entry(C.Structure):
     _fields_ = [("container", C.c_uint32), ("type_key", C.c_char_p), ("uuid", C.c_char_p),
-                ("idx", C.c_int32), ("usedmem", C.c_int32), ("usedcores", C.c_int32)]
+                ("idx", C.c_int32), ("usedmem", C.c_int32), ("usedcores", C.c_int32),
+                ("mig_profile", C.c_char_p), ("mig_start", C.c_uint32), ("mig_size", C.c_uint32)]
 
 
 class hs_failed_node(C.Structure):
@@ -216,13 +257,14 @@ def build_node(node):
     "pair_scores": [[int]] | None, "device_cordon": str | None, "hami_vnpu_core": -1|0|1}"""
     devs = node["devices"]
     arr = (hs_device_info * max(1, len(devs)))()
+    keep = [arr]
     for i, d in enumerate(devs):
+        mp, nmp = build_mig_profiles(d.get("mig_profiles"), keep)
         arr[i] = hs_device_info(_b(d["id"]), d.get("index", i), d.get("count", 0), d.get("devmem", 0),
                                 d.get("devcore", 0), _b(d.get("type", "")), d.get("numa", 0), _b(d.get("mode", "")),
                                 1 if d.get("health", True) else 0, _b(d.get("vendor", "NVIDIA")),
-                                d.get("network_id", -1))
+                                d.get("network_id", -1), mp, nmp)
     ps = None
-    keep = [arr]
     if node.get("pair_scores") is not None:
         n = len(devs)
         flat = (C.c_int32 * max(1, n * n))()
@@ -263,7 +305,8 @@ def _s(p):
 
 
 def read_result(res):
-    """hs_filter_result -> dict. devices: {type_key: [[(uuid, idx, usedmem, usedcores), ...] per container]}"""
+    """hs_filter_result -> dict. devices: {type_key: [[(uuid, idx, usedmem, usedcores), ...] per container]}; a pick
+    on a GPU in MIG mode carries its reservation too: (uuid, idx, usedmem, usedcores, profile, start, size)"""
     out = {"status": res.status, "node_index": res.node_index, "node": _s(res.node_name), "score": res.score,
            "devices": {}, "annotations": {}, "failed": {}}
     for i in range(res.n_entries):
@@ -272,7 +315,10 @@ def read_result(res):
         while len(lst) <= e.container:
             lst.append([])
         if e.uuid is not None:
-            lst[e.container].append((_s(e.uuid), e.idx, e.usedmem, e.usedcores))
+            row = (_s(e.uuid), e.idx, e.usedmem, e.usedcores)
+            if e.mig_profile is not None:
+                row += (_s(e.mig_profile), e.mig_start, e.mig_size)
+            lst[e.container].append(row)
     for i in range(res.n_annotations):
         out["annotations"][_s(res.annotations[i].key)] = _s(res.annotations[i].value)
     for i in range(res.n_failed):

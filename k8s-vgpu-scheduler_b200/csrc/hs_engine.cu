@@ -124,7 +124,16 @@ struct DevSlot {
   int32_t count = 0, devmem = 0, devcore = 0, numa = 0, network_id = -1;
   bool health = true;
   int type_id = 0, mode_id = 0, vendor_id = 0;
+  int mig_geom = 0;         // index into hs_handle::mig_geoms for a GPU in MIG mode (0 = the empty geometry)
 };
+
+// One distinct MigProfiles list (device.MigProfile, devices.go:79-90) and what the device needs of it (MigGeom)
+struct MigGeomHost {
+  struct Prof { std::string name; int32_t memory_mb, core; uint32_t slice_count; std::vector<std::pair<uint32_t, uint32_t>> placements; };
+  std::vector<Prof> profiles;   // as registered
+  MigGeom dev;
+};
+struct MigRes { std::string uuid, profile; uint32_t start = 0, size = 0; };   // one entry of hami.io/vgpu-mig-allocations
 
 struct NodeSlot {
   std::string name;
@@ -134,6 +143,8 @@ struct NodeSlot {
   std::string cordon;
   int vnpu = -1;
   std::vector<std::string> base_types;  // nodeDeviceBaseTypes, score.go:71-79 (sorted, unique)
+  bool has_mig = false;        // some device is in MIG mode
+  bool mig_touched = false;    // the last mig_refresh left MIG bookkeeping in the node's dflags
 };
 
 struct VendorInfo {
@@ -160,6 +171,8 @@ struct PodRec {           // podManager entry: what to subtract when the pod goe
   bool init_released = false;   // PodInfo.InitContainerResourceReleased (pods.go:40-53)
   std::string ns;               // pod.Namespace, for quotaManager.RmUsage
   std::vector<std::pair<std::string, int4>> parked;   // usage on devices that left the node's register annotation, by UUID
+  uint8_t n_ent[HS_D] = {0, 0, 0, 0, 0, 0, 0, 0};     // cached ContainerDevice entries per device slot (getNodesUsage visits each one)
+  std::vector<MigRes> mig;                            // decoded hami.io/vgpu-mig-allocations, annotation order
 };
 
 struct EntryMeta {
@@ -224,6 +237,12 @@ struct hs_handle {
   std::vector<std::string> types, types_lower, types_upper;
   std::unordered_map<std::string, int> type_ids;
   std::vector<std::string> modes;
+  // dynamic MIG: distinct profile lists, their device table, and whether any GPU in MIG mode is registered
+  std::deque<MigGeomHost> mig_geoms;
+  MigGeom* d_mig_tab = nullptr;
+  size_t mig_tab_uploaded = 0;
+  bool has_mig = false;
+  size_t n_mig_pods = 0;       // cached pods that carry reservations
 
   std::vector<NodeSlot> nodes;
   std::deque<std::string> name_store;      // node names at stable addresses (slot order)
@@ -457,6 +476,14 @@ inline cudaError_t down_sync(hs_handle* h, void* dst, const void* src, size_t by
 }
 
 int flush_inventory(hs_handle* h) {
+  if (h->has_mig && h->mig_tab_uploaded != h->mig_geoms.size()) {      // the MIG geometry table: 16 x 272 B, rewritten when a new one appears
+    if (!h->d_mig_tab) CUDA_OK(h, cudaMalloc(&h->d_mig_tab, 16 * sizeof(MigGeom)));
+    std::vector<MigGeom> tab(16);
+    memset(tab.data(), 0, 16 * sizeof(MigGeom));
+    for (size_t g = 0; g < h->mig_geoms.size() && g < 16; g++) tab[g] = h->mig_geoms[g].dev;
+    CUDA_OK(h, cudaMemcpy(h->d_mig_tab, tab.data(), 16 * sizeof(MigGeom), cudaMemcpyHostToDevice));
+    h->mig_tab_uploaded = h->mig_geoms.size();
+  }
   if (h->dirty_hi < h->dirty_lo) return HS_OK;
   size_t t0 = (size_t)h->dirty_lo, nt = (size_t)(h->dirty_hi - h->dirty_lo + 1);
   size_t o = t0 * HS_D * HS_TILE, n = nt * HS_D * HS_TILE;
@@ -724,6 +751,19 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
               !(e.flags & EF_ASCEND910C)) ? 1 : 0;
     if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX | EF_NEURON))) p.fast = 0;
   }
+  if (h->has_mig)       // dynamic MIG lives in the general evaluator: every NVIDIA request of a handle that holds a GPU in MIG mode
+    for (const DevEntry& e : c.entries) {
+      if (e.vendor != HV_NVIDIA) continue;
+      p.fast = 0;
+      if (!(e.flags & EF_MIGMODE_OK)) continue;      // the pod pins another mode: it never reaches a MIG GPU's placements
+      if (e.nums > HS_D) { h->err = "more than 8 MIG instances in one request"; return HS_ERR_UNSUPPORTED; }
+      if (p.flags & PF_TOPOLOGY) {
+        // topology-aware Fit on a MIG GPU keeps visiting it until its placements run out and then chooses among all
+        // (GPU, placement) candidates by pair score (nvidia/device.go:831-870): more candidates than the evaluator's lists hold
+        h->err = "topology-aware requests on a handle with GPUs in MIG mode are outside the built scope";
+        return HS_ERR_UNSUPPORTED;
+      }
+    }
   quota_rows_for(h, c.meta.ns, p);
   if (p.q_idx[0] >= 0 || p.q_idx[1] >= 0) p.fast = 0;   // the quota check lives in the general evaluator (hs_eval.cuh)
   c.meta.kind = OP_FILTER;
@@ -762,6 +802,157 @@ void apply_host_delta(hs_handle* h, int node, const int4* delta, int sign) {
   h->h_tot[node].y = host_node_score_bits(h, node);
 }
 
+// ---- dynamic MIG, host side ------------------------------------------------------------------------------------
+// The device table entry for one MigProfiles list: selectMigCandidate's stable (MemoryMB, SliceCount) order, each
+// candidate with the placements of the FIRST profile of its name (findMigProfile, mig_topology.go:42-49) in
+// selectMigPlacement's order (descending start for "1g." / "3g." names, ascending otherwise; stable).
+int intern_geom(hs_handle* h, const hs_mig_profile* profiles, uint32_t n, std::string& err) {
+  if (n > 16) { err = "a GPU in MIG mode reports more than 16 MIG profiles"; return -1; }
+  MigGeomHost g;
+  for (uint32_t i = 0; i < n; i++) {
+    MigGeomHost::Prof p;
+    p.name = profiles[i].name ? profiles[i].name : "";
+    p.memory_mb = profiles[i].memory_mb; p.core = profiles[i].core; p.slice_count = profiles[i].slice_count;
+    if (profiles[i].n_placements > 8) { err = "a MIG profile reports more than 8 placements"; return -1; }
+    if (p.core > 32767 || p.core < -32768) { err = "MIG profile core share outside int16"; return -1; }
+    for (uint32_t j = 0; j < profiles[i].n_placements; j++) {
+      const hs_mig_placement& q = profiles[i].placements[j];
+      if (q.size == 0) { err = "a MIG placement of size 0 never conflicts: the reference's Fit would visit the GPU forever (nvidia/device.go:846-848)"; return -1; }
+      if (q.start > 7 || q.size > 8 || q.start + q.size > 8) { err = "MIG placement outside the engine's 8-slice mask"; return -1; }
+      p.placements.emplace_back(q.start, q.size);
+    }
+    g.profiles.push_back(p);
+  }
+  for (size_t k = 0; k < h->mig_geoms.size(); k++) {
+    const auto& o = h->mig_geoms[k].profiles;
+    if (o.size() != g.profiles.size()) continue;
+    bool same = true;
+    for (size_t i = 0; i < o.size() && same; i++)
+      same = o[i].name == g.profiles[i].name && o[i].memory_mb == g.profiles[i].memory_mb && o[i].core == g.profiles[i].core &&
+             o[i].slice_count == g.profiles[i].slice_count && o[i].placements == g.profiles[i].placements;
+    if (same) return (int)k;
+  }
+  if (h->mig_geoms.size() >= 16) { err = "more than 15 distinct MIG geometries on one handle"; return -1; }
+  memset(&g.dev, 0, sizeof g.dev);
+  std::vector<int> order(g.profiles.size());
+  for (size_t i = 0; i < order.size(); i++) order[i] = (int)i;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+    if (g.profiles[a].memory_mb != g.profiles[b].memory_mb) return g.profiles[a].memory_mb < g.profiles[b].memory_mb;
+    return g.profiles[a].slice_count < g.profiles[b].slice_count;
+  });
+  g.dev.n_cand = (uint32_t)order.size();
+  for (size_t c = 0; c < order.size(); c++) {
+    const auto& cp = g.profiles[order[c]];
+    int first = order[c];
+    for (size_t i = 0; i < g.profiles.size(); i++) if (g.profiles[i].name == cp.name) { first = (int)i; break; }
+    auto pl = g.profiles[first].placements;
+    const bool high = cp.name.compare(0, 3, "1g.") == 0 || cp.name.compare(0, 3, "3g.") == 0;
+    std::stable_sort(pl.begin(), pl.end(), [&](const std::pair<uint32_t, uint32_t>& a, const std::pair<uint32_t, uint32_t>& b) {
+      return high ? a.first > b.first : a.first < b.first;
+    });
+    MigCand& mc = g.dev.cand[c];
+    mc.mem = cp.memory_mb; mc.core = (int16_t)cp.core; mc.prof = (uint8_t)order[c];
+    mc.n_place = (uint8_t)pl.size();
+    for (size_t j = 0; j < pl.size(); j++) mc.place[j] = (uint8_t)((pl[j].first << 4) | pl[j].second);
+  }
+  h->mig_geoms.push_back(g);
+  return (int)h->mig_geoms.size() - 1;
+}
+
+inline uint32_t mig_res_mask(uint32_t start, uint32_t size) {
+  uint32_t m = 0;
+  for (uint32_t b = start; b < 8 && b - start < size; b++) m |= 1u << b;
+  return m;
+}
+
+// What ONE cached pod does to the MIG state of its node (the pod's share of getNodesUsage, scheduler.go:757-842):
+// occ[d] = slices its reservations cover on device d, bad[d] = 1 when it makes the device fail closed.
+void mig_pod_effect(const hs_handle* h, const NodeSlot& ns, const PodRec& pr, uint8_t* occ, uint8_t* bad) {
+  for (int d = 0; d < HS_D; d++) { occ[d] = 0; bad[d] = 0; }
+  const size_t nd = std::min(ns.devs.size(), (size_t)HS_D);
+  std::vector<char> taken(pr.mig.size(), 0);
+  for (size_t d = 0; d < nd; d++) {
+    const DevSlot& ds = ns.devs[d];
+    for (int k = 0; k < (int)pr.n_ent[d]; k++) {
+      size_t r = 0;
+      while (r < pr.mig.size() && (taken[r] || pr.mig[r].uuid != ds.uuid)) r++;
+      if (r < pr.mig.size()) {
+        if (ds.mode == "hami-core") { bad[d] = 1; continue; }         // :788-792 (the reservation is not consumed)
+        taken[r] = 1;
+        occ[d] |= (uint8_t)mig_res_mask(pr.mig[r].start, pr.mig[r].size);
+        continue;
+      }
+      if (ds.mode == "mig") bad[d] = 1;                                // :799-802
+    }
+  }
+  for (size_t r = 0; r < pr.mig.size(); r++) {                         // :810-841, reservations nothing consumed
+    if (taken[r]) continue;
+    bool matched = false;
+    for (size_t d = 0; d < nd; d++) {
+      if (ns.devs[d].uuid != pr.mig[r].uuid) continue;
+      matched = true;
+      if (ns.devs[d].mode != "mig") bad[d] = 1;
+      else occ[d] |= (uint8_t)mig_res_mask(pr.mig[r].start, pr.mig[r].size);
+      break;
+    }
+    if (!matched)
+      for (size_t d = 0; d < nd; d++) if (ns.devs[d].mode == "mig") bad[d] = 1;
+  }
+  (void)h;
+}
+
+// The node's MIG state from the pod cache, leaving out the pods in `without`: occ / bad per device slot.  Returns
+// false when the node has no GPU in MIG mode and no cached pod with reservations touches it (nothing to keep).
+bool mig_node_state(const hs_handle* h, int slot, const std::unordered_set<std::string>* without, uint8_t* occ, int* bad) {
+  for (int d = 0; d < HS_D; d++) { occ[d] = 0; bad[d] = 0; }
+  const NodeSlot& ns = h->nodes[slot];
+  if (!ns.has_mig && h->n_mig_pods == 0) return false;
+  bool any = ns.has_mig;
+  for (const auto& kv : h->pods) {
+    if (kv.second.node != slot) continue;
+    if (!ns.has_mig && kv.second.mig.empty()) continue;
+    if (without && without->count(kv.first)) continue;
+    uint8_t o[HS_D], b[HS_D];
+    mig_pod_effect(h, ns, kv.second, o, b);
+    for (int d = 0; d < HS_D; d++) { occ[d] |= o[d]; bad[d] += b[d]; }
+    any = true;
+  }
+  return any;
+}
+
+inline uint32_t mig_dflags(uint32_t df, uint32_t occ, int bad) {
+  bad = bad > 255 ? 255 : bad;
+  df = (df & 0x0000ffffu) | (occ << 16) | ((uint32_t)bad << 24);
+  return (bad == 0 && (df & DF_HEALTH_REG)) ? (df | DF_HEALTH) : (df & ~DF_HEALTH);
+}
+
+// Bring the node's dflags (host mirror) in line with the pod cache; true when something changed.
+bool mig_refresh(hs_handle* h, int slot) {
+  NodeSlot& ns = h->nodes[slot];
+  uint8_t occ[HS_D]; int bad[HS_D];
+  const bool any = mig_node_state(h, slot, nullptr, occ, bad);
+  if (!any && !ns.mig_touched) return false;
+  ns.mig_touched = any;
+  bool changed = false;
+  for (int d = 0; d < HS_D; d++) {
+    int4& v = h->h_dyn[inv_idx(slot, d)];
+    const uint32_t nf = mig_dflags((uint32_t)v.w, occ[d], bad[d]);
+    if (nf != (uint32_t)v.w) { v.w = (int)nf; changed = true; }
+  }
+  return changed;
+}
+
+// encoding/json string: quotes, backslash, control characters and the HTML trio escaped
+std::string json_string(const char* v) {
+  std::string o = "\"";
+  for (const unsigned char* p = (const unsigned char*)(v ? v : ""); *p; p++) {
+    if (*p == '"' || *p == '\\') { o += '\\'; o += (char)*p; }
+    else if (*p < 0x20 || *p == '<' || *p == '>' || *p == '&') { char b[8]; snprintf(b, sizeof b, "\\u%04x", *p); o += b; }
+    else o += (char)*p;
+  }
+  return o + "\"";
+}
+
 std::string encode_pod_single(const std::vector<std::vector<const hs_alloc_entry*>>& pd, const NodeSlot* type_from = nullptr) {
   // EncodePodSingleDevice / EncodeContainerDevices, devices.go:451-484.  type_from: the vendor's picks carry the
   // DEVICE's type string instead of k.Type (amd/device.go:341-346)
@@ -798,7 +989,12 @@ const std::string& fail_string_slow(hs_handle* h, const DevFail& f) {
   if (it != h->reason_cache.end()) return it->second;
   std::string s;
   uint32_t kind = f.kind_cards & 15u, cards = f.kind_cards >> 4;
-  if (kind == FK_NODE_INSUFFICIENT) s = "NodeInsufficientDevice";
+  if (kind == FK_MIG_ADD_FAILED) {        // score.go:125-128 + nvidia/device.go:649
+    std::string uuid;
+    if (f.c1 < h->nodes.size() && cards < h->nodes[f.c1].devs.size()) uuid = h->nodes[f.c1].devs[cards].uuid;
+    s = "AddResourceUsage failed for device " + uuid + ": MIG profile and placement allocation failed";
+  }
+  else if (kind == FK_NODE_INSUFFICIENT) s = "NodeInsufficientDevice";
   else if (kind == FK_TYPE_NOT_FOUND) s = "Device type not found";
   else if (kind == FK_HIST) {
     // common.GenReason, common/common.go:46-53
@@ -819,6 +1015,7 @@ const std::string& fail_string_slow(hs_handle* h, const DevFail& f) {
 int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_cap) {
   memset(&ka, 0, sizeof ka);
   ka.dyn = h->d_dyn; ka.stat = h->d_stat; ka.node_flags = h->d_flags; ka.node_tot = h->d_tot; ka.pair = h->d_pair;
+  ka.mig_tab = h->has_mig ? h->d_mig_tab : nullptr;
   ka.n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
   ka.cand_pos = h->have_cand ? h->b_candpos.d : nullptr;
   ka.pods = h->b_pods.d; ka.entries = h->b_entries.d; ka.uuid_pool = h->b_uuid.d; ka.rel_pool = h->b_rel.d;
@@ -1113,7 +1310,7 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
     // request's type key holding the rows, plus one empty list under every other base type of the node
     // (score.go:278-282), and the annotation map to four keys.  Same output as the general code, no maps.
     if (m.n_ctr == 1 && m.n_init == 0 && m.entries.size() == 1 && (m.entries[0].vendor == 0 || m.entries[0].vendor == 1) &&
-        h->b_entries.h[h->b_pods.h[op].entry_off].nums > 0) {
+        h->b_entries.h[h->b_pods.h[op].entry_off].nums > 0 && !ns.has_mig) {
       const EntryMeta& em = m.entries[0];
       const VendorInfo& v = h->vendors[em.vendor];
       bool placed = false;
@@ -1121,7 +1318,7 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
         if (dec.n_alloc == 0) { h->r_entries.push_back(hs_alloc_entry{0, em.type.c_str(), nullptr, 0, 0, 0}); return; }
         for (uint32_t i = 0; i < dec.n_alloc; i++) {
           const DevAlloc& a = h->b_alloc.h[dec.alloc_off + i];
-          const DevSlot& ds = ns.devs[a.dev];
+          const DevSlot& ds = ns.devs[AL_DEV(a)];
           h->r_entries.push_back(hs_alloc_entry{0, em.type.c_str(), ds.uuid.c_str(), (int32_t)ds.index, a.usedmem, (int32_t)a.usedcores});
         }
       };
@@ -1142,7 +1339,7 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
       };
       for (uint32_t i = 0; i < dec.n_alloc; i++) {
         const DevAlloc& a = h->b_alloc.h[dec.alloc_off + i];
-        buf += ns.devs[a.dev].uuid; buf += ','; buf += em.type; buf += ',';
+        buf += ns.devs[AL_DEV(a)].uuid; buf += ','; buf += em.type; buf += ',';
         put_int(a.usedmem); buf += ','; put_int((int)a.usedcores); buf += ':';
       }
       buf += ';';
@@ -1159,9 +1356,18 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
     std::vector<std::vector<hs_alloc_entry>> rows(m.entries.size());
     for (uint32_t i = 0; i < dec.n_alloc; i++) {
       const DevAlloc& a = h->b_alloc.h[dec.alloc_off + i];
-      const EntryMeta& em = m.entries[a.entry];
-      const DevSlot& ds = ns.devs[a.dev];
-      rows[a.entry].push_back(hs_alloc_entry{0, em.type.c_str(), ds.uuid.c_str(), (int32_t)ds.index, a.usedmem, (int32_t)a.usedcores});
+      const EntryMeta& em = m.entries[AL_ENTRY(a)];
+      const DevSlot& ds = ns.devs[AL_DEV(a)];
+      hs_alloc_entry row{0, em.type.c_str(), ds.uuid.c_str(), (int32_t)ds.index, a.usedmem, (int32_t)a.usedcores, nullptr, 0, 0};
+      if (AL_MIG(a) && ds.mig_geom > 0 && (size_t)ds.mig_geom < h->mig_geoms.size()) {
+        // CustomInfo["migProfile"] / ["migPlacement"] of the pick (nvidia/device.go:653-657)
+        const MigGeomHost& g = h->mig_geoms[ds.mig_geom];
+        const MigCand& mc = g.dev.cand[AL_MIG_CAND(a)];
+        const uint8_t pl = mc.place[AL_MIG_PLACE(a)];
+        row.mig_profile = g.profiles[mc.prof].name.c_str();
+        row.mig_start = pl >> 4; row.mig_size = pl & 15u;
+      }
+      rows[AL_ENTRY(a)].push_back(row);
     }
     // scoreNode's PodDevices bookkeeping incl. the base-type padding (score.go:226-286,334-338)
     typedef std::vector<std::vector<hs_alloc_entry>> PSD;
@@ -1246,6 +1452,19 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
       }
       annos[v.to_allocate] = s;
       annos[v.allocated] = s;
+      if (v.word == "NVIDIA") {   // EncodeMigAllocations, nvidia/device.go:511-513, nvidia/mig_allocations.go:48-76
+        std::string mig;
+        for (size_t c = 0; c < it->second.size(); c++)
+          for (size_t di = 0; di < it->second[c].size(); di++) {
+            const hs_alloc_entry* e = it->second[c][di];
+            if (!e->mig_profile || !e->mig_profile[0] || e->mig_size == 0) continue;
+            mig += mig.empty() ? "[" : ",";
+            mig += "{\"containerIndex\":" + std::to_string(c) + ",\"deviceIndex\":" + std::to_string(di) + ",\"gpuUUID\":" +
+                   json_string(e->uuid) + ",\"profile\":" + json_string(e->mig_profile) + ",\"placement\":{\"start\":" +
+                   std::to_string(e->mig_start) + ",\"size\":" + std::to_string(e->mig_size) + "}}";
+          }
+        if (!mig.empty()) annos["hami.io/vgpu-mig-allocations"] = mig + "]";
+      }
       if (v.ascend) {  // ascend/device.go:221-253
         annos["predicate-time"] = "";
         std::string json;
@@ -1353,7 +1572,18 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
     }
     p.rel_node = it->second.node;
     p.rel_off = (int32_t)rel.size();
-    for (int d = 0; d < HS_D; d++) rel.push_back(it->second.delta[d]);
+    for (int d = 0; d < HS_D; d++) { int4 v = it->second.delta[d]; v.w = 0; rel.push_back(v); }
+    if (h->nodes[it->second.node].has_mig || !it->second.mig.empty()) {
+      // MIG bookkeeping of the release (PF_REL_MIG): whether this pod was one of those that make a device fail closed,
+      // and the slices still covered by the reservations of the pods that remain (pods released earlier in this
+      // batch are gone; pods committed in this batch carry no reservation yet)
+      uint8_t o[HS_D], b[HS_D], occ[HS_D]; int bad[HS_D];
+      mig_pod_effect(h, h->nodes[it->second.node], it->second, o, b);
+      released.insert(uid);
+      mig_node_state(h, it->second.node, &released, occ, bad);
+      for (int d = 0; d < HS_D; d++) rel[(size_t)p.rel_off + d].w = (int)((b[d] ? 1u : 0u) | 2u | ((uint32_t)occ[d] << 8));
+      p.flags |= PF_REL_MIG;
+    }
     {   // the same rows inside the op record (RelDelta over e0): the resident owner needs no second fetch
       RelDelta rd[HS_D];
       bool fits = true;
@@ -1387,25 +1617,37 @@ void absorb_results(hs_handle* h, int first, int last) {
     if (m.kind == OP_FILTER && m.status == HS_OK && dec.status == 0 && !m.dry) {
       PodRec pr;
       pr.node = dec.node;
-      for (int d = 0; d < HS_D; d++) pr.delta[d] = h->b_delta.h[(size_t)op * HS_D + d];
+      for (int d = 0; d < HS_D; d++) {
+        pr.delta[d] = h->b_delta.h[(size_t)op * HS_D + d];
+        pr.n_ent[d] = pr.delta[d].x > 0 ? 1 : 0;      // collapsed: one cached entry per device (initContainer.go:36-114)
+        pr.delta[d].w = 0;
+      }
       apply_host_delta(h, dec.node, pr.delta, +1);
       pr.ns = m.ns;
       quota_track(h, m.ns, dec.node, pr.delta, +1);
       h->pods[m.uid] = pr;
+      if (h->nodes[dec.node].has_mig) mig_refresh(h, dec.node);
     } else if (m.kind == OP_RELEASE) {
       const DevPod& p = h->b_pods.h[op];
       if (p.rel_node >= 0) {
         apply_host_delta(h, p.rel_node, h->b_rel.h + p.rel_off, -1);
         quota_track(h, m.ns, p.rel_node, h->b_rel.h + p.rel_off, -1);
         auto known = h->pods.find(m.uid);  // podManager.DelPod: only now, with the device's release done
-        if (known != h->pods.end()) { h->n_parked -= known->second.parked.size(); h->pods.erase(known); }
+        if (known != h->pods.end()) {
+          h->n_parked -= known->second.parked.size();
+          if (!known->second.mig.empty()) h->n_mig_pods--;
+          h->pods.erase(known);
+        }
+        if (p.flags & PF_REL_MIG) mig_refresh(h, p.rel_node);
       } else {
         auto it = h->pods.find(m.uid);
         if (it != h->pods.end()) {
           apply_host_delta(h, it->second.node, it->second.delta, -1);
           quota_track(h, it->second.ns, it->second.node, it->second.delta, -1);
           h->n_parked -= it->second.parked.size();
+          const int rel_node = it->second.node;
           h->pods.erase(it);
+          if (h->nodes[rel_node].has_mig) mig_refresh(h, rel_node);
         }
       }
     }
@@ -1523,7 +1765,7 @@ int job_stage(hs_handle* h, BatchJob& j, StageMark& mark, WaitIdle wait_idle) {
   if (h->b_entries.cap != ce) { staged.entries = 0; mark.entries = 0; }
   if (h->b_uuid.cap != cu) { staged.uuid = 0; mark.uuid = 0; }
   if (h->b_rel.cap != cr) { staged.rel = 0; mark.rel = 0; }
-  mark_windows(j.pods, staged.pods);
+  if (!h->has_mig) mark_windows(j.pods, staged.pods);      // the window resolver does not carry the MIG bookkeeping of a release
   memcpy(h->b_pods.h + staged.pods, j.pods.data() + staged.pods, (j.pods.size() - staged.pods) * sizeof(DevPod));
   if (j.entries.size() > staged.entries) memcpy(h->b_entries.h + staged.entries, j.entries.data() + staged.entries, (j.entries.size() - staged.entries) * sizeof(DevEntry));
   if (j.uuid_pool.size() > staged.uuid) memcpy(h->b_uuid.h + staged.uuid, j.uuid_pool.data() + staged.uuid, (j.uuid_pool.size() - staged.uuid) * sizeof(uint32_t));
@@ -1993,6 +2235,7 @@ void hs_destroy(hs_handle* h) {
   for (int p = 0; p < 8; p++)        // peer mailboxes opened with cudaIpcOpenMemHandle; our own is a plain allocation
     if (h->mbox_peer[p] && h->mbox_peer[p] != h->d_mbox) cudaIpcCloseMemHandle(h->mbox_peer[p]);
   if (h->d_mbox) cudaFree(h->d_mbox);
+  if (h->d_mig_tab) cudaFree(h->d_mig_tab);
   if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
   for (int i = 0; i < 4; i++) { if (h->ck0[i]) cudaEventDestroy(h->ck0[i]); if (h->ck1[i]) cudaEventDestroy(h->ck1[i]); if (h->cc[i]) cudaEventDestroy(h->cc[i]); if (h->cu[i]) cudaEventDestroy(h->cu[i]); }
   if (h->stream3) cudaStreamDestroy(h->stream3);
@@ -2020,7 +2263,12 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
     s.uuid = d.id ? d.id : ""; s.type = d.type ? d.type : ""; s.mode = d.mode ? d.mode : ""; s.vendor = d.vendor ? d.vendor : "";
     s.index = d.index; s.count = d.count; s.devmem = d.devmem; s.devcore = d.devcore; s.numa = d.numa;
     s.network_id = d.network_id; s.health = d.health != 0;
-    if (s.mode == "mig") { h->err = "MIG-mode devices are outside the built scope (dynamic MIG placement)"; return HS_ERR_UNSUPPORTED; }
+    if (s.mode == "mig") {
+      if (h->shard_world > 1) { h->err = "GPUs in MIG mode are not supported on the sharded (multi-GPU) path"; return HS_ERR_UNSUPPORTED; }
+      if (h->mig_geoms.empty()) { std::string e; intern_geom(h, nullptr, 0, e); }     // geometry 0: no profile at all
+      s.mig_geom = intern_geom(h, d.mig_profiles, d.mig_profiles ? d.n_mig_profiles : 0, h->err);
+      if (s.mig_geom < 0) return HS_ERR_UNSUPPORTED;
+    }
     if (s.numa < 0 || s.numa > 255 || s.index > 255 || s.network_id > 254) { h->err = "numa/index/NetworkID out of the packed range"; return HS_ERR_UNSUPPORTED; }
     s.type_id = intern_type(h, s.type);
     if (s.type_id < 0) { h->err = "more distinct device types than HS_MAX_TYPES"; return HS_ERR_UNSUPPORTED; }
@@ -2087,8 +2335,10 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
         if (kv.second.node != slot) continue;
         int4 moved[HS_D];
         for (int k = 0; k < HS_D; k++) moved[k] = make_int4(0, 0, 0, 0);
+        uint8_t ment[HS_D] = {0, 0, 0, 0, 0, 0, 0, 0};
         for (size_t d = 0; d < ns.devs.size() && d < (size_t)HS_D; d++) {
           const int4& v = kv.second.delta[d];
+          if (new_of[d] >= 0) ment[new_of[d]] = kv.second.n_ent[d];
           if (new_of[d] >= 0) moved[new_of[d]] = v;
           else if (v.x | v.y | v.z) { kv.second.parked.emplace_back(ns.devs[d].uuid, v); h->n_parked++; }
         }
@@ -2099,17 +2349,22 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
             for (size_t i = 0; i < pk.size();) {
               if (pk[i].first != sorted[k].uuid) { i++; continue; }
               moved[k].x += pk[i].second.x; moved[k].y += pk[i].second.y; moved[k].z += pk[i].second.z;
+              if (ment[k] == 0) ment[k] = 1;
               revived[k].x += pk[i].second.x; revived[k].y += pk[i].second.y; revived[k].z += pk[i].second.z;
               pk.erase(pk.begin() + (long)i);
               h->n_parked--;
             }
           }
-        for (int k = 0; k < HS_D; k++) kv.second.delta[k] = moved[k];
+        for (int k = 0; k < HS_D; k++) { kv.second.delta[k] = moved[k]; kv.second.n_ent[k] = ment[k]; }
       }
   }
   if (!ns.alive) { h->n_alive++; }
   ns.alive = true;
   ns.devs = sorted;
+  ns.has_mig = false;
+  for (const auto& d : ns.devs) if (d.mode == "mig") ns.has_mig = true;
+  if (ns.has_mig) h->has_mig = true;
+  ns.mig_touched = ns.mig_touched || ns.has_mig;
   ns.has_cordon = node->device_cordon != nullptr;
   ns.cordon = node->device_cordon ? node->device_cordon : "";
   ns.vnpu = node->hami_vnpu_core;
@@ -2130,11 +2385,12 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
       auto ou = old_usage.find(s.uuid);
       if (ou != old_usage.end()) { dy.x = ou->second.x; dy.y = ou->second.y; dy.z = ou->second.z; }
       else { dy.x = revived[d].x; dy.y = revived[d].y; dy.z = revived[d].z; }
-      uint32_t df = DF_PRESENT | (s.health ? DF_HEALTH : 0u) | (cordoned.count(s.uuid) ? DF_CORDON : 0u) |
+      uint32_t df = DF_PRESENT | (s.health ? (DF_HEALTH | DF_HEALTH_REG) : 0u) | (cordoned.count(s.uuid) ? DF_CORDON : 0u) |
                     ((uint32_t)s.mode_id << 3) | ((uint32_t)(s.network_id >= 0 ? s.network_id : 255) << 8);
       dy.w = (int)df;
       st.x = s.count; st.y = s.devmem; st.z = s.devcore;
-      st.w = (int)((uint32_t)s.numa | ((uint32_t)s.type_id << 8) | ((uint32_t)s.index << 14) | ((uint32_t)s.vendor_id << 22));
+      st.w = (int)((uint32_t)s.numa | ((uint32_t)s.type_id << 8) | ((uint32_t)s.index << 14) | ((uint32_t)s.vendor_id << 22) |
+                   ((uint32_t)s.mig_geom << 27));
       h->uuid_index[s.uuid].push_back(((uint32_t)slot << 8) | (uint32_t)d);
     }
     h->h_dyn[inv_idx(slot, d)] = dy;
@@ -2179,6 +2435,7 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
   {
     h->h_tot[slot] = make_int4((int)nf, host_node_score_bits(h, slot), 0, 0);
   }
+  mig_refresh(h, slot);       // reservations in use and fail-closed devices, from the pods the cache holds for this node
   mark_dirty(h, slot);
   return HS_OK;
 }
@@ -2231,8 +2488,10 @@ int32_t hs_usage_apply(hs_handle* h, const char* pod_uid, const char* node, cons
     delta[d] = make_int4(std::max(slots, 1), usedmem, usedcores, 0);
     apply_host_delta(h, slot, delta, +1);
     pit->second.delta[d].x += delta[d].x; pit->second.delta[d].y += delta[d].y; pit->second.delta[d].z += delta[d].z;
+    if (pit->second.n_ent[d] < 255) pit->second.n_ent[d]++;
     matched = true;
   }
+  mig_refresh(h, slot);
   mark_dirty(h, slot);
   return matched ? HS_OK : HS_ERR_NOTFOUND;
 }
@@ -2246,8 +2505,47 @@ int32_t hs_pod_delete(hs_handle* h, const char* pod_uid) {
   quota_track(h, it->second.ns, it->second.node, it->second.delta, -1);
   mark_dirty(h, it->second.node);
   h->n_parked -= it->second.parked.size();
+  if (!it->second.mig.empty()) h->n_mig_pods--;
+  const int del_node = it->second.node;
   h->pods.erase(it);
+  mig_refresh(h, del_node);
   return HS_OK;
+}
+
+// The informer re-delivers a cached pod with its reservations decoded (pi.Pod = pod, pods.go:76-77; read by
+// getNodesUsage, scheduler.go:757-842)
+int32_t hs_pod_set_mig(hs_handle* h, const char* pod_uid, const hs_mig_reservation* res, uint32_t n) {
+  if (!h || !pod_uid || (!res && n)) return HS_ERR_INVALID;
+  HS_IDLE(h);
+  auto it = h->pods.find(pod_uid);
+  if (it == h->pods.end()) return HS_ERR_NOTFOUND;
+  if (!it->second.mig.empty()) h->n_mig_pods--;
+  it->second.mig.clear();
+  for (uint32_t i = 0; i < n; i++) {
+    MigRes r;
+    r.uuid = res[i].gpu_uuid ? res[i].gpu_uuid : ""; r.profile = res[i].profile ? res[i].profile : "";
+    r.start = res[i].start; r.size = res[i].size;
+    it->second.mig.push_back(r);
+  }
+  if (!it->second.mig.empty()) h->n_mig_pods++;
+  h->nodes[it->second.node].mig_touched = true;
+  mig_refresh(h, it->second.node);
+  mark_dirty(h, it->second.node);
+  return HS_OK;
+}
+
+int32_t hs_snapshot_node_mig(hs_handle* h, const char* node, uint32_t* occupied, uint8_t* health, uint32_t cap) {
+  if (!h || !node) return HS_ERR_INVALID;
+  HS_IDLE(h);
+  auto it = h->node_by_name.find(node);
+  if (it == h->node_by_name.end()) return HS_ERR_NOTFOUND;
+  const NodeSlot& ns = h->nodes[it->second];
+  for (size_t d = 0; d < ns.devs.size() && d < cap; d++) {
+    const uint32_t df = (uint32_t)h->h_dyn[inv_idx(it->second, (int)d)].w;
+    if (occupied) occupied[d] = DF_OCC(df);
+    if (health) health[d] = (df & DF_HEALTH) ? 1 : 0;
+  }
+  return (int32_t)ns.devs.size();
 }
 
 int32_t hs_rollback(hs_handle* h, const char* pod_uid) { return hs_pod_delete(h, pod_uid); }

@@ -401,6 +401,23 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
     if (etc - w.cores[d] < fc.cores) { REASON(5); continue; }
     if (etc == 100 && fc.cores == 100 && w.used[d] > 0) { REASON(9); continue; }
     if (etc != 0 && w.cores[d] == etc && fc.cores == 0) { REASON(3); continue; }
+    const bool migDev = isNv && DF_MODE(df) == DF_MODE_MIG;
+    if (migDev) {
+      // CustomFilterRule, nvidia/device.go:602-619 with the resolved memory (:811-814): the picks this Fit already queued
+      // on the same GPU take their placements first, then the request must still find a profile with a free placement
+      bool ok = ka.mig_tab != nullptr;
+      if (ok) {
+        const MigGeom& g = ka.mig_tab[PK_GEOM(pk)];
+        uint32_t occ = DF_OCC(df);
+        for (int t = 0; t < fc.ntmp && ok; t++) {
+          if (fc.tmp_dev[t] != d) continue;
+          const int sel = hs_mig_select(g, occ, fc.tmp_mem[t]);
+          if (sel < 0) ok = false; else occ |= (uint32_t)sel >> 8;
+        }
+        if (ok) ok = hs_mig_select(g, occ, memreq) >= 0;
+      }
+      if (!ok) { REASON(11 /*CardMigTopologyInfeasible*/); continue; }
+    }
     // customFilterRule, mthreads/device.go:266-276,362-366: the pod's earlier containers all sit on this very card
     if ((e.flags & EF_MTHREADS) && (w.mth_prev & ~(1u << d))) { REASON(10); continue; }
     if (k_nums > 0) {
@@ -410,6 +427,7 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
       fc.ntmp++;
     }
     if (k_nums == 0 && decrement) return true;
+    if (migDev && fc.ntmp < HS_D) i++;      // nvidia/device.go:846-848: a GPU in MIG mode is visited again for the next instance
   }
 
   if (is910CMulti) {
@@ -555,10 +573,10 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
       const int d = ord_get(w.order, i);
       if ((e.type_contains >> PK_TYPE(w.packed[d])) & 1ull) {
         td[cnt++] = d;
-        if (DF_MODE(w.dflags[d]) == 2u) anyMig = true;
+        if (DF_MODE(w.dflags[d]) == DF_MODE_MIG) anyMig = true;
       }
     }
-    // isMIGRequest, score.go:54-69 (MIG devices are refused at upsert, so anyMig is false)
+    // isMIGRequest, score.go:54-69
     const bool migReq = e.vendor == HV_NVIDIA && (e.flags & EF_MIGMODE_OK) && anyMig;
     if (e.nums > cnt && !migReq) {
       if (MODE == EV_EXPLAIN) out.fkind = FK_NODE_INSUFFICIENT;
@@ -575,7 +593,20 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
     bool missing_net = false;
     for (int t = 0; t < fc.ntmp; t++) {
       const int d = fc.tmp_dev[t];
-      const int pick_cores = (e.flags & (EF_AMD | EF_NEURON)) ? fc.tmp_cores[t] : fc.cores;
+      int pick_cores = (e.flags & (EF_AMD | EF_NEURON)) ? fc.tmp_cores[t] : fc.cores;
+      int mig_sel = -1;
+      if (e.vendor == HV_NVIDIA && DF_MODE(w.dflags[d]) == DF_MODE_MIG) {
+        // AddResourceUsage on a GPU in MIG mode (nvidia/device.go:645-659): the pick becomes the chosen profile
+        mig_sel = ka.mig_tab != nullptr ? hs_mig_select(ka.mig_tab[PK_GEOM(w.packed[d])], DF_OCC(w.dflags[d]), fc.tmp_mem[t]) : -1;
+        if (mig_sel < 0) {
+          if (MODE == EV_EXPLAIN) { out.fkind = FK_MIG_ADD_FAILED; out.fcards = (uint32_t)d; }
+          return false;
+        }
+        const MigCand& mc = ka.mig_tab[PK_GEOM(w.packed[d])].cand[mig_sel & 15];
+        fc.tmp_mem[t] = mc.mem;
+        pick_cores = mc.core;
+        w.dflags[d] |= ((uint32_t)mig_sel >> 8) << 16;      // MigAllocationsInUse of the working copy
+      }
       if (e.flags & EF_NEURON) {          // awsneuron/device.go:340-355
         if (w.aws[d] < 0) w.aws[d] = 0;
         w.aws[d] += fc.tmp_aws[t];
@@ -587,6 +618,7 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
         DevAlloc a;
         a.entry = (uint8_t)(ei);
         a.dev = (uint8_t)d;
+        if (mig_sel >= 0) { a.entry |= (uint8_t)((mig_sel & 15) << 4); a.dev |= (uint8_t)(8u | (((uint32_t)mig_sel >> 4) & 7u) << 4); }
         a.usedcores = (int16_t)pick_cores;
         a.usedmem = fc.tmp_mem[t];
         out.allocs[out.n_alloc++] = a;
@@ -636,7 +668,8 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
 
   if (pod.n_init > 0) {
     int bu[HS_D], bm[HS_D], bc[HS_D];
-    for (int d = 0; d < w.ndev; d++) { bu[d] = w.used[d]; bm[d] = w.mem[d]; bc[d] = w.cores[d]; }
+    uint32_t bf[HS_D];       // dflags carry the working copy's MIG reservations
+    for (int d = 0; d < w.ndev; d++) { bu[d] = w.used[d]; bm[d] = w.mem[d]; bc[d] = w.cores[d]; bf[d] = w.dflags[d]; }
     for (int c = 0; c < pod.n_init && c < pod.n_ctr; c++) {
       const int eb = pod.ctr_begin[c], ee = pod.ctr_begin[c + 1];
       if (eb == ee) {          // len(req) == 0: every base type gets an empty container (score.go:233-238; the rows are padded on the host)
@@ -647,7 +680,7 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
       for (int d = 0; d < HS_D; d++) w.aws[d] = -1;
       if (!dev_fit_container<MODE>(w, pod, ent, eb, ee, node, nflags, ka, out, score_acc, &score_zero, qa)) return false;
       if (qa) for (int v = 0; v < 2; v++) if (base_key[v] && qa->len[v] == c) qa->len[v]++;   // score.go:246-250
-      for (int d = 0; d < w.ndev; d++) { w.used[d] = bu[d]; w.mem[d] = bm[d]; w.cores[d] = bc[d]; }
+      for (int d = 0; d < w.ndev; d++) { w.used[d] = bu[d]; w.mem[d] = bm[d]; w.cores[d] = bc[d]; w.dflags[d] = bf[d]; }
     }
   }
   w.order = identity;

@@ -343,7 +343,39 @@ bool decode_node_json(const std::string& s, std::vector<Device>& out, std::strin
         if (v.kind == JV::Num && num_to_int(v, 64, false, n)) { if (n != (int32_t)n) bad("numa does not fit the engine's int32"); d.numa = (int32_t)n; }
         else bad(type_err(v, "numa", "int"));
       }
-      else if (key_is(k, "migProfiles")) { if (v.kind == JV::Arr) d.has_mig_profiles = !v.a.empty(); else bad(type_err(v, "migProfiles", "[]device.MigProfile")); }
+      else if (key_is(k, "migProfiles")) {
+        if (v.kind == JV::Null) { d.has_mig_profiles = false; d.mig_profiles.clear(); continue; }
+        if (v.kind != JV::Arr) { bad(type_err(v, "migProfiles", "[]device.MigProfile")); continue; }
+        d.has_mig_profiles = !v.a.empty();
+        d.mig_profiles.clear();
+        for (const JV& pj : v.a) {      // device.MigProfile, devices.go:79-90
+          MigProfileRec pr;
+          if (pj.kind != JV::Obj) { if (pj.kind != JV::Null) bad(type_err(pj, "migProfiles", "device.MigProfile")); d.mig_profiles.push_back(pr); continue; }
+          for (const auto& f : pj.o) {
+            int64_t x = 0;
+            if (key_is(f.first, "name")) { if (f.second.kind == JV::Str) pr.name = f.second.s; else if (f.second.kind != JV::Null) bad(type_err(f.second, "migProfiles.name", "string")); }
+            else if (key_is(f.first, "memoryMB")) { if (f.second.kind == JV::Num && num_to_int(f.second, 32, false, x)) pr.memory_mb = (int32_t)x; else if (f.second.kind != JV::Null) bad(type_err(f.second, "migProfiles.memoryMB", "int32")); }
+            else if (key_is(f.first, "core")) { if (f.second.kind == JV::Num && num_to_int(f.second, 32, false, x)) pr.core = (int32_t)x; else if (f.second.kind != JV::Null) bad(type_err(f.second, "migProfiles.core", "int32")); }
+            else if (key_is(f.first, "sliceCount")) { if (f.second.kind == JV::Num && num_to_int(f.second, 32, true, x)) pr.slice_count = (uint32_t)x; else if (f.second.kind != JV::Null) bad(type_err(f.second, "migProfiles.sliceCount", "uint32")); }
+            else if (key_is(f.first, "placements")) {
+              if (f.second.kind == JV::Null) { pr.placements.clear(); continue; }
+              if (f.second.kind != JV::Arr) { bad(type_err(f.second, "migProfiles.placements", "[]device.MigPlacement")); continue; }
+              pr.placements.clear();
+              for (const JV& qj : f.second.a) {
+                MigPlacementRec q;
+                if (qj.kind == JV::Obj)
+                  for (const auto& g : qj.o) {
+                    if (key_is(g.first, "start")) { if (g.second.kind == JV::Num && num_to_int(g.second, 32, true, x)) q.start = (uint32_t)x; else if (g.second.kind != JV::Null) bad(type_err(g.second, "migProfiles.placements.start", "uint32")); }
+                    else if (key_is(g.first, "size")) { if (g.second.kind == JV::Num && num_to_int(g.second, 32, true, x)) q.size = (uint32_t)x; else if (g.second.kind != JV::Null) bad(type_err(g.second, "migProfiles.placements.size", "uint32")); }
+                  }
+                else if (qj.kind != JV::Null) bad(type_err(qj, "migProfiles.placements", "device.MigPlacement"));
+                pr.placements.push_back(q);
+              }
+            }
+          }
+          d.mig_profiles.push_back(pr);
+        }
+      }
       else if (key_is(k, "migtemplate")) { if (v.kind != JV::Arr) bad(type_err(v, "migtemplate", "[]device.Geometry")); }
       else if (key_is(k, "custominfo")) {
         if (v.kind != JV::Obj) { bad(type_err(v, "custominfo", "map[string]interface {}")); continue; }
@@ -369,6 +401,56 @@ bool decode_node_json(const std::string& s, std::vector<Device>& out, std::strin
 // false on ANY error, as the caller there turns every error into 0: a syntax error, a document that is not an object
 // (null is fine and leaves the map empty), a key strconv.ParseInt rejects, a value that is not an integer number
 // (null is fine and stores 0).  A later duplicate key wins.
+// nvidia.DecodeMigAllocations, nvidia/mig_allocations.go:78-112
+bool decode_mig_allocations(const std::string& json, std::vector<MigReservationRec>& out, std::string& err) {
+  out.clear();
+  if (json.empty()) return true;
+  JParser p(json);
+  JV doc;
+  if (!p.document(doc)) { err = p.err; return false; }
+  if (doc.kind == JV::Null) return true;
+  if (doc.kind != JV::Arr) { err = std::string("json: cannot unmarshal ") + kind_name(doc) + " into Go value of type []nvidia.MigAllocation"; return false; }
+  std::vector<std::pair<int64_t, int64_t>> seen;
+  size_t i = 0;
+  for (const JV& el : doc.a) {
+    MigReservationRec r;
+    int64_t ci = 0, di = 0, x = 0;
+    bool has_uuid = false, has_gi = false, has_ci = false;
+    if (el.kind == JV::Obj)
+      for (const auto& f : el.o) {
+        const JV& v = f.second;
+        auto fail = [&](const char* field, const char* gotype) {
+          err = std::string("json: cannot unmarshal ") + kind_name(v) + " into Go struct field MigAllocation." + field + " of type " + gotype;
+        };
+        if (key_is(f.first, "containerIndex")) { if (v.kind == JV::Num && num_to_int(v, 64, false, x)) ci = x; else if (v.kind != JV::Null) { fail("containerIndex", "int"); return false; } }
+        else if (key_is(f.first, "deviceIndex")) { if (v.kind == JV::Num && num_to_int(v, 64, false, x)) di = x; else if (v.kind != JV::Null) { fail("deviceIndex", "int"); return false; } }
+        else if (key_is(f.first, "gpuUUID")) { if (v.kind == JV::Str) r.gpu_uuid = v.s; else if (v.kind != JV::Null) { fail("gpuUUID", "string"); return false; } }
+        else if (key_is(f.first, "profile")) { if (v.kind == JV::Str) r.profile = v.s; else if (v.kind != JV::Null) { fail("profile", "string"); return false; } }
+        else if (key_is(f.first, "migUUID")) { if (v.kind == JV::Str) has_uuid = !v.s.empty(); else if (v.kind != JV::Null) { fail("migUUID", "string"); return false; } }
+        else if (key_is(f.first, "gpuInstanceID")) { if (v.kind == JV::Num && num_to_int(v, 32, true, x)) has_gi = true; else if (v.kind == JV::Null) has_gi = false; else { fail("gpuInstanceID", "uint32"); return false; } }
+        else if (key_is(f.first, "computeInstanceID")) { if (v.kind == JV::Num && num_to_int(v, 32, true, x)) has_ci = true; else if (v.kind == JV::Null) has_ci = false; else { fail("computeInstanceID", "uint32"); return false; } }
+        else if (key_is(f.first, "placement")) {
+          if (v.kind == JV::Obj) {
+            for (const auto& g : v.o) {
+              if (key_is(g.first, "start")) { if (g.second.kind == JV::Num && num_to_int(g.second, 32, true, x)) r.start = (uint32_t)x; else if (g.second.kind != JV::Null) { err = "json: cannot unmarshal into Go struct field MigAllocation.placement.start of type uint32"; return false; } }
+              else if (key_is(g.first, "size")) { if (g.second.kind == JV::Num && num_to_int(g.second, 32, true, x)) r.size = (uint32_t)x; else if (g.second.kind != JV::Null) { err = "json: cannot unmarshal into Go struct field MigAllocation.placement.size of type uint32"; return false; } }
+            }
+          } else if (v.kind != JV::Null) { fail("placement", "device.MigPlacement"); return false; }
+        }
+      }
+    else if (el.kind != JV::Null) { err = std::string("json: cannot unmarshal ") + kind_name(el) + " into Go value of type nvidia.MigAllocation"; return false; }
+    if (ci < 0 || di < 0 || r.gpu_uuid.empty() || r.profile.empty() || r.size == 0) { err = "MIG allocation " + std::to_string(i) + " is incomplete"; return false; }
+    const int runtime = (has_uuid ? 1 : 0) + (has_gi ? 1 : 0) + (has_ci ? 1 : 0);
+    if (runtime != 0 && runtime != 3) { err = "MIG allocation " + std::to_string(i) + " has partial runtime identity"; return false; }
+    for (auto& k : seen)
+      if (k.first == ci && k.second == di) { err = "duplicate MIG allocation for container " + std::to_string(ci) + " device " + std::to_string(di); return false; }
+    seen.emplace_back(ci, di);
+    out.push_back(r);
+    i++;
+  }
+  return true;
+}
+
 bool decode_int_map(const std::string& s, std::vector<std::pair<int64_t, int64_t>>& out) {
   out.clear();
   JParser p(s);

@@ -7,6 +7,15 @@
 
 namespace hs_ingest {
 
+struct MigPlacementRec { uint32_t start = 0, size = 0; };
+struct MigProfileRec {     // device.MigProfile (devices.go:79-90), json: name / memoryMB / core / sliceCount / placements
+  std::string name;
+  int32_t memory_mb = 0, core = 0;
+  uint32_t slice_count = 0;
+  std::vector<MigPlacementRec> placements;
+};
+struct MigReservationRec { std::string gpu_uuid, profile; uint32_t start = 0, size = 0; };
+
 struct Device {            // device.DeviceInfo, the fields the scheduler path reads (devices.go:127-144)
   std::string id, type, mode, vendor;
   uint32_t index = 0;
@@ -14,6 +23,7 @@ struct Device {            // device.DeviceInfo, the fields the scheduler path r
   bool health = false;
   int32_t network_id = -1; // CustomInfo["NetworkID"] (Ascend), -1 = absent
   bool has_mig_profiles = false;
+  std::vector<MigProfileRec> mig_profiles;   // DeviceInfo.MIGProfiles
   bool die_strategy = false; // CustomInfo["DeviceStrategy"] == "die" (vastai die mode)
   bool has_aic = false;      // CustomInfo["AIC"] is a string: the card the die sits on (vastai/device.go:374-387)
   std::string aic;
@@ -35,6 +45,10 @@ bool devices_from_capacity(int kind, const std::string& node, int64_t cores, int
 // awsneuron GetNodeDevices (awsneuron/device.go:156-198); cores_per 0 = derive from this node; network_id = 1 on "inf" nodes else 0
 bool neuron_devices_from_capacity(const std::string& node, int64_t counts, int64_t cores_total, int64_t cores_per, const char* instance_type,
                                   std::vector<Device>& out, std::string& err);
+// nvidia.DecodeMigAllocations (nvidia/mig_allocations.go:78-112): the hami.io/vgpu-mig-allocations annotation; "" decodes
+// to no reservation; false + err on malformed JSON, an incomplete entry, a partial runtime identity or a duplicate
+// (containerIndex, deviceIndex) — the caller then treats the pod as carrying no reservation (scheduler.go:760-766)
+bool decode_mig_allocations(const std::string& json, std::vector<MigReservationRec>& out, std::string& err);
 // json.Unmarshal into map[int]int as parseMetaxAnnos uses it (metax/device.go:168-183): false on any error
 bool decode_int_map(const std::string& json, std::vector<std::pair<int64_t, int64_t>>& out);
 // scores[i*n+j] = Scores[devs[j].id] of the pair-score record whose uuid is devs[i].id (0 where absent)

@@ -56,15 +56,17 @@ __device__ void collapse_rows(const DevEntry* ent, const DevAlloc* al, uint32_t 
   for (int d = 0; d < HS_D; d++) delta[d] = make_int4(0, 0, 0, 0);
   // groups are (type key, device); visit each group once at its first row
   for (uint32_t i = 0; i < n; i++) {
-    const int key = ent[al[i].entry].key_id, dev = al[i].dev;
+    const int key = ent[AL_ENTRY(al[i])].key_id, dev = AL_DEV(al[i]);
     bool first = true;
     for (uint32_t j = 0; j < i; j++)
-      if (ent[al[j].entry].key_id == key && al[j].dev == dev) { first = false; break; }
+      if (ent[AL_ENTRY(al[j])].key_id == key && AL_DEV(al[j]) == dev) { first = false; break; }
     if (!first) continue;
+    // a pick on a GPU in MIG mode: the cached pod carries no reservation yet, so the GPU fails closed (.w bit 0)
+    if (AL_MIG(al[i])) delta[dev].w = 1;
     int imem = 0, icores = 0, islots = 0, amem = 0, acores = 0, aslots = 0;
     for (uint32_t j = i; j < n; j++) {
-      if (ent[al[j].entry].key_id != key || al[j].dev != dev) continue;
-      if (ent[al[j].entry].is_init) {
+      if (ent[AL_ENTRY(al[j])].key_id != key || AL_DEV(al[j]) != dev) continue;
+      if (ent[AL_ENTRY(al[j])].is_init) {
         if (al[j].usedmem > imem) imem = al[j].usedmem;
         if ((int)al[j].usedcores > icores) icores = (int)al[j].usedcores;
         islots = 1;
@@ -100,12 +102,25 @@ __device__ __forceinline__ void quota_apply(const KernelArgs& ka, const DevPod& 
   }
 }
 
+// dflags after a change of the MIG bookkeeping (delta.w of a commit / release row): bit 0 = one more (sign +1) or one
+// less cached pod that makes the device fail closed, bit 1 = the covered slices become bits 8-15
+__device__ __forceinline__ uint32_t mig_apply(uint32_t df, int w, int sign) {
+  if (w & 2) df = (df & ~(255u << 16)) | (((uint32_t)w >> 8) & 255u) << 16;
+  if (w & 1) {
+    int bad = (int)DF_BAD(df) + sign;
+    bad = bad < 0 ? 0 : (bad > 255 ? 255 : bad);
+    df = (df & 0x00ffffffu) | ((uint32_t)bad << 24);
+  }
+  return (DF_BAD(df) == 0u && (df & DF_HEALTH_REG)) ? (df | DF_HEALTH) : (df & ~DF_HEALTH);
+}
+
 __device__ __forceinline__ void store_usage(const KernelArgs& ka, int node, const int4* delta, int sign) {
   int4* dy = ka.dyn + (size_t)node * HS_D;
   for (int d = 0; d < HS_D; d++) {
-    if (delta[d].x == 0 && delta[d].y == 0 && delta[d].z == 0) continue;
+    if (delta[d].x == 0 && delta[d].y == 0 && delta[d].z == 0 && delta[d].w == 0) continue;
     int4 v = dy[d];
     v.x += sign * delta[d].x; v.y += sign * delta[d].y; v.z += sign * delta[d].z;
+    if (delta[d].w) v.w = (int)mig_apply((uint32_t)v.w, delta[d].w, sign);
     dy[d] = v;
   }
 }
@@ -136,6 +151,11 @@ __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
     for (int r = 8; r < 15; r++) c1 |= (out.reasons[r] & 15u) << (4 * (r - 8));
   }
   f.c0 = c0; f.c1 = c1; f.pad = 0;
+}
+// FK_MIG_ADD_FAILED names a device of the node in its text: the node slot rides along (fcards holds the device slot)
+__device__ __forceinline__ void pack_fail_node(const EvalOut& out, DevFail& f, int node) {
+  pack_fail(out, f);
+  if (out.fkind == FK_MIG_ADD_FAILED) f.c1 = (uint32_t)node;
 }
 
 // Arg-best + grid barrier in one 16-byte L2 slot per op: {best key, arrivals}.  Warp 0 of every CTA
@@ -444,17 +464,20 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
         if (pod.rel_node >= 0) {          // known pod: the rows came with the op record (no second fetch)
           const RelDelta rd = reinterpret_cast<const RelDelta*>(&pod.e0)[glane];
           delta = make_int4((int)rd.slots, rd.mem, (int)rd.cores, 0);
+          if (pod.flags & PF_REL_MIG) delta.w = rows[glane].w;     // MIG bookkeeping rides in the pool rows only
         } else {
           delta = rows[glane];
         }
-        if (delta.x | delta.y | delta.z) {
+        if (delta.x | delta.y | delta.z | delta.w) {
           int4* p = ka.dyn + (size_t)node * HS_D + glane;
           if (resident) {                 // the registers are the current copy: store, do not read-modify-write
             D.used -= delta.x; D.mem -= delta.y; D.cores -= delta.z;
+            if (delta.w) D.dflags = mig_apply(D.dflags, delta.w, -1);
             *p = make_int4(D.used, D.mem, D.cores, (int)D.dflags);
           } else {
             int4 v = *p;
             v.x -= delta.x; v.y -= delta.y; v.z -= delta.z;
+            if (delta.w) v.w = (int)mig_apply((uint32_t)v.w, delta.w, -1);
             *p = v;
           }
         }
@@ -749,7 +772,7 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
             out.fkind = FK_NONE; out.fcards = 0;
             float sc;
             dev_score_node<EV_EXPLAIN>(w, pod, ent, (uint32_t)node, nf, ka, out, &sc);
-            pack_fail(out, f);
+            pack_fail_node(out, f, node);
           }
           fb[node] = f;
         }

@@ -21,13 +21,20 @@
 // so a warp that owns one tile reads each (d) row as one coalesced 512 B line
 // group with 128-bit loads.  32 B per device, 256 B per node.
 //
-// dflags: bit0 health | bit1 cordoned | bit2 present | bits3-5 mode id | bits8-15 NetworkID (255 = none)
-// packed: bits0-7 numa | bits8-13 type id | bits14-21 DeviceInfo.Index | bits22-26 vendor id
+// dflags: bit0 health (as getNodesUsage would hand it to Fit) | bit1 cordoned | bit2 present | bits3-5 mode id |
+//         bit6 health as registered | bits8-15 NetworkID (255 = none) | bits16-23 MIG slices covered by the reservations
+//         in use | bits24-31 number of cached pods that make the device fail closed (scheduler.go:788-841)
+// packed: bits0-7 numa | bits8-13 type id | bits14-21 DeviceInfo.Index | bits22-26 vendor id | bits27-30 MIG geometry (0 = none)
 #define DF_HEALTH 1u
 #define DF_CORDON 2u
 #define DF_PRESENT 4u
 #define DF_MODE(x) (((x) >> 3) & 7u)
 #define DF_NET(x) (((x) >> 8) & 255u)
+#define DF_HEALTH_REG 64u
+#define DF_MODE_MIG 2u              // index of "mig" in the handle's mode table (fixed: "", "hami-core", "mig", "mps")
+#define DF_OCC(x) (((x) >> 16) & 255u)
+#define DF_BAD(x) ((x) >> 24)
+#define PK_GEOM(x) (((x) >> 27) & 15u)
 #define PK_NUMA(x) ((int)((x) & 255u))
 #define PK_TYPE(x) (((x) >> 8) & 63u)
 #define PK_INDEX(x) ((int)(((x) >> 14) & 255u))
@@ -85,6 +92,8 @@ struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 
 #define PF_NUMA_ASSERT 8u   // nvidia.com/numa-bind parses true (assertNuma)
 #define PF_ASCEND_HAMICORE 16u // huawei.com/vnpu-mode == "hami-core"
 #define PF_NODE_BINPACK 64u // node policy == "binpack" (metax ScoreNode reads the policy string, metax/device.go:192-211)
+#define PF_REL_MIG 128u   // OP_RELEASE of a known pod that touches MIG state: the release pool rows carry it in .w (bit0: one
+                          // fail-closed count less, bit1: set the covered slices to bits 8-15)
 #define PF_DRYRUN 32u     // decide and report the devices, leave the inventory untouched (filterSimulation, scheduler.go:1156-1199)
 
 enum { OP_FILTER = 0, OP_RELEASE = 1, OP_NOP = 2 };
@@ -141,12 +150,38 @@ HS_HD inline bool hs_verdict_needs_order(const DevPod& p) {
          !(p.sort_mode == SORT_MUTEX && !(p.flags & PF_TOPOLOGY));
 }
 
+// Dynamic MIG (nvidia/device.go:602-664, nvidia/mig_topology.go): what selectMigCandidate needs of one GPU's
+// MigProfiles, prepared on the host — the candidates in its stable (MemoryMB, SliceCount) order, each with the placements
+// of the FIRST profile of that name (findMigProfile) in selectMigPlacement's order (descending start for 1g./3g.).
+// place = (start << 4) | size, start + size <= 8, so a placement is an 8-bit slice mask.
+struct MigCand { int32_t mem; int16_t core; uint8_t n_place; uint8_t prof; uint8_t place[8]; };
+struct MigGeom { uint32_t n_cand; uint32_t pad[3]; MigCand cand[16]; };
+static_assert(sizeof(MigCand) == 16 && sizeof(MigGeom) == 272, "MIG geometry table layout");
+HS_HD inline uint32_t hs_mig_mask(uint8_t place) { return (((1u << (place & 15u)) - 1u) << (place >> 4)) & 255u; }
+// selectMigCandidate: -1 = none, else candidate | placement index << 4 | slice mask << 8
+HS_HD inline int hs_mig_select(const MigGeom& g, uint32_t occupied, int memory) {
+  for (uint32_t c = 0; c < g.n_cand && c < 16u; c++) {
+    if (g.cand[c].mem < memory) continue;
+    for (int p = 0; p < (int)g.cand[c].n_place && p < 8; p++) {
+      const uint32_t m = hs_mig_mask(g.cand[c].place[p]);
+      if (!(m & occupied)) return (int)c | (p << 4) | (int)(m << 8);
+    }
+  }
+  return -1;
+}
+
 struct DevAlloc {           // one ContainerDevice, 8 B
-  uint8_t entry;            // index into the pod's entries (container + type)
-  uint8_t dev;              // device slot on the node
+  uint8_t entry;            // bits 0-3: index into the pod's entries (container + type); bits 4-7: MIG candidate (AL_MIG only)
+  uint8_t dev;              // bits 0-2: device slot on the node; bit 3: a pick on a GPU in MIG mode; bits 4-6: its placement
   int16_t usedcores;
   int32_t usedmem;
 };
+
+#define AL_ENTRY(a) ((int)((a).entry & 15u))
+#define AL_DEV(a) ((int)((a).dev & 7u))
+#define AL_MIG(a) (((a).dev & 8u) != 0)
+#define AL_MIG_CAND(a) ((int)((a).entry >> 4))
+#define AL_MIG_PLACE(a) ((int)(((a).dev >> 4) & 7u))
 
 struct DevDecision {        // 16 B header; rows live in the alloc pool
   int32_t status;           // 0 fit, 1 no fit, 2 release/nop done, <0 error
@@ -159,7 +194,8 @@ struct DevDecision {        // 16 B header; rows live in the alloc pool
 };
 
 // per-node failure record written only when a decision finds no node (common.go:46-53)
-enum { FK_NONE = 0, FK_HIST = 1, FK_NODE_INSUFFICIENT = 2, FK_TYPE_NOT_FOUND = 3, FK_NOT_CANDIDATE = 4 };
+enum { FK_NONE = 0, FK_HIST = 1, FK_NODE_INSUFFICIENT = 2, FK_TYPE_NOT_FOUND = 3, FK_NOT_CANDIDATE = 4,
+       FK_MIG_ADD_FAILED = 5 };   // AddResourceUsage returned an error (score.go:125-128): c0 = device slot, c1 = node slot
 struct DevFail {            // 16 B
   uint32_t kind_cards;      // bits0-3 kind | bits4-31 cards denominator
   uint32_t c0;              // reasons 0-7, 4 bits each (HS_R_* order)
@@ -181,6 +217,7 @@ struct KernelArgs {
   const uint32_t* node_flags;
   int4* node_tot;               // per node {flags, float bits of ComputeDefaultScore on the current usage, 0, 0}: kept current by every commit/release
   const int16_t* pair;          // [node][64]
+  const MigGeom* mig_tab;       // MIG geometries by PK_GEOM (entry 0 is empty); NULL while no GPU in MIG mode is registered
   int32_t n_nodes;              // slots (padded to HS_TILE)
   // candidate positions: NULL = every alive node, position == slot
   const int32_t* cand_pos;      // per slot: position in NodeNames or -1

@@ -17,7 +17,7 @@ _lib = None
 EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_run_batch_async", "hs_batch_wait", "hs_batch_get", "hs_rollback",
-    "hs_snapshot_node", "hs_pod_get", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
+    "hs_snapshot_node", "hs_pod_get", "hs_pod_set_mig", "hs_snapshot_node_mig", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
     "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect",
     "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_filter_dry", "hs_filter_simulate", "hs_quota_set", "hs_quota_del", "hs_quota_get", "hs_quota_memory_factor", "hs_generate_requests", "hs_debug_timing", "hs_debug_window_stats", "hs_debug_decision_ns", "hs_debug_copy_bytes", "hs_debug_host_seconds", "hs_debug_divcheck", "hs_debug_metax_table",
 ]
@@ -55,6 +55,8 @@ def lib():
     L.hs_rollback.argtypes = [C.c_void_p, C.c_char_p]
     L.hs_snapshot_node.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_device_usage_row), C.c_uint32]
     L.hs_pod_get.argtypes = [C.c_void_p, C.c_char_p, P(C.c_char_p), P(abi.hs_pod_usage_row), C.c_uint32]
+    L.hs_pod_set_mig.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_mig_reservation), C.c_uint32]
+    L.hs_snapshot_node_mig.argtypes = [C.c_void_p, C.c_char_p, P(C.c_uint32), P(C.c_uint8), C.c_uint32]
     L.hs_decode_node_devices.argtypes = [P(abi.hs_vendor_registration), P(P(abi.hs_device_info)), P(C.c_uint32), P(P(C.c_int32))]
     L.hs_decode_pod_devices.argtypes = [P(abi.hs_kv), C.c_uint32, P(abi.hs_kv), C.c_uint32, P(P(abi.hs_pod_device)), P(C.c_uint32)]
     L.hs_collapse_pod_devices.argtypes = [C.c_int32, C.c_uint32, P(abi.hs_pod_device), C.c_uint32, P(P(abi.hs_pod_device)), P(C.c_uint32)]
@@ -344,6 +346,19 @@ class Engine:
         if n < 0:
             return None
         return node.value.decode(), [(rows[i].uuid.decode(), rows[i].slots, rows[i].usedmem, rows[i].usedcores) for i in range(n)]
+
+    def pod_set_mig(self, uid, reservations):
+        """The informer delivers the pod's decoded hami.io/vgpu-mig-allocations: [(gpu_uuid, profile, start, size)]."""
+        keep = []
+        arr, n = abi.build_mig_reservations(reservations, keep)
+        return self.L.hs_pod_set_mig(self.h, abi._b(uid), arr, n)
+
+    def snapshot_node_mig(self, node, cap=16):
+        """[(occupied slice mask, healthy)] per device of the node, as getNodesUsage would hand them to Fit."""
+        occ = (C.c_uint32 * cap)()
+        hl = (C.c_uint8 * cap)()
+        n = self.L.hs_snapshot_node_mig(self.h, abi._b(node), occ, hl, cap)
+        return [(occ[i], hl[i]) for i in range(max(0, min(n, cap)))]
 
     def decision_ns(self, n):
         """%globaltimer ns at which each Filter decision of the last run_batch became final (0 = not a Filter)."""

@@ -8,6 +8,7 @@
 #include <cassert>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <set>
 #include <stdexcept>
 #include <thread>
@@ -351,11 +352,106 @@ std::string EncodePodSingleDevice(const PodSingleDevice& pd) {
 // cambricon/device.go:378-488, ascend/device.go:442-617 are one loop with
 // per-vendor gates; the gates are spelled out per vendor below.
 // ---------------------------------------------------------------------------
-void Devices::AddResourceUsage(DeviceUsage& n, const ContainerDevice& ctr) const {
+bool Devices::AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const {
   // nvidia/device.go:645-664 (non-MIG), hygon:257, cambricon:338, ascend:426
   n.Used = i32add(n.Used, 1);
   n.Usedcores = i32add(n.Usedcores, ctr.Usedcores);
   n.Usedmem = i32add(n.Usedmem, ctr.Usedmem);
+  return true;
+}
+
+// ---- dynamic MIG: nvidia/mig_topology.go ---------------------------------------------------
+static bool migPlacementsOverlap(const MigPlacement& a, const MigPlacement& b) {   // mig_topology.go:78-80
+  return (uint64_t)a.Start < (uint64_t)b.Start + b.Size && (uint64_t)b.Start < (uint64_t)a.Start + a.Size;
+}
+static std::vector<MigPlacement> orderedMigPlacements(const std::string& profile, std::vector<MigPlacement> ordered) {   // :30-40
+  const bool high = HasPrefix(profile, "1g.") || HasPrefix(profile, "3g.");    // preferHighMigPlacement, :26-28
+  std::stable_sort(ordered.begin(), ordered.end(), [&](const MigPlacement& a, const MigPlacement& b) {
+    return high ? a.Start > b.Start : a.Start < b.Start;
+  });
+  return ordered;
+}
+bool SelectMigPlacement(const std::vector<MigProfile>& profiles, const std::vector<MigPlacement>& occupied,
+                        const std::string& profileName, MigPlacement& out) {       // :57-76
+  const MigProfile* profile = nullptr;
+  for (auto& p : profiles) if (p.Name == profileName) { profile = &p; break; }    // findMigProfile, :42-49
+  if (!profile) return false;
+  for (auto& candidate : orderedMigPlacements(profileName, profile->Placements)) {
+    bool conflict = false;
+    for (auto& existing : occupied) if (migPlacementsOverlap(candidate, existing)) { conflict = true; break; }
+    if (!conflict) { out = candidate; return true; }
+  }
+  return false;
+}
+bool SelectMigCandidate(const std::vector<MigProfile>& profiles, const std::vector<MigPlacement>& occupied, int32_t memory,
+                        MigProfile& profile, MigPlacement& placement) {           // nvidia/device.go:621-639
+  std::vector<MigProfile> candidates = profiles;
+  std::stable_sort(candidates.begin(), candidates.end(), [](const MigProfile& a, const MigProfile& b) {
+    if (a.MemoryMB != b.MemoryMB) return a.MemoryMB < b.MemoryMB;
+    return a.SliceCount < b.SliceCount;
+  });
+  for (auto& c : candidates) {
+    if (c.MemoryMB < memory) continue;
+    if (SelectMigPlacement(profiles, occupied, c.Name, placement)) { profile = c; return true; }
+  }
+  return false;
+}
+bool CanPlaceMigProfiles(const std::vector<MigProfile>& capabilities, const std::vector<MigPlacement>& occupied,
+                         const std::vector<std::string>& requested) {             // mig_topology.go:85-132
+  if (requested.empty()) return true;
+  std::map<std::string, std::vector<MigPlacement>> placements;
+  for (auto& p : capabilities) placements[p.Name] = p.Placements;
+  std::vector<std::string> ordered = requested;
+  std::stable_sort(ordered.begin(), ordered.end(), [&](const std::string& a, const std::string& b) {
+    const auto& left = placements[a]; const auto& right = placements[b];
+    if (left.size() != right.size()) return left.size() < right.size();
+    if (left.empty()) return false;
+    return left[0].Size > right[0].Size;
+  });
+  std::vector<MigPlacement> used = occupied;
+  std::function<bool(size_t)> place = [&](size_t idx) {
+    if (idx == ordered.size()) return true;
+    for (auto& candidate : orderedMigPlacements(ordered[idx], placements[ordered[idx]])) {
+      bool conflict = false;
+      for (auto& existing : used) if (migPlacementsOverlap(candidate, existing)) { conflict = true; break; }
+      if (conflict) continue;
+      used.push_back(candidate);
+      if (place(idx + 1)) return true;
+      used.pop_back();
+    }
+    return false;
+  };
+  return place(0);
+}
+static std::vector<MigPlacement> occupiedMigPlacements(const std::vector<MigAllocation>& allocations) {   // :51-57
+  std::vector<MigPlacement> out;
+  for (auto& a : allocations) out.push_back(a.Placement);
+  return out;
+}
+// EncodeMigAllocations, nvidia/mig_allocations.go:48-76 (encoding/json: struct field order, omitempty runtime fields absent)
+static std::string jsonString(const std::string& v) {
+  std::string o = "\"";
+  for (unsigned char c : v) {
+    if (c == '"' || c == '\\') { o += '\\'; o += (char)c; }
+    else if (c == '<' || c == '>' || c == '&') { char b[8]; snprintf(b, sizeof b, "\\u%04x", c); o += b; }   // encoding/json escapes HTML
+    else if (c < 0x20) { char b[8]; snprintf(b, sizeof b, "\\u%04x", c); o += b; }
+    else o += (char)c;
+  }
+  return o + "\"";
+}
+std::string EncodeMigAllocations(const PodSingleDevice& pd) {
+  std::string out;
+  int n = 0;
+  for (size_t containerIndex = 0; containerIndex < pd.size(); containerIndex++)
+    for (size_t deviceIndex = 0; deviceIndex < pd[containerIndex].size(); deviceIndex++) {
+      const ContainerDevice& dev = pd[containerIndex][deviceIndex];
+      if (!dev.HasMig || dev.MigProfileName.empty() || dev.MigPlace.Size == 0) continue;
+      out += n++ ? "," : "";
+      out += "{\"containerIndex\":" + std::to_string(containerIndex) + ",\"deviceIndex\":" + std::to_string(deviceIndex) +
+             ",\"gpuUUID\":" + jsonString(dev.UUID) + ",\"profile\":" + jsonString(dev.MigProfileName) +
+             ",\"placement\":{\"start\":" + std::to_string(dev.MigPlace.Start) + ",\"size\":" + std::to_string(dev.MigPlace.Size) + "}}";
+    }
+  return n ? "[" + out + "]" : "";
 }
 
 namespace {
@@ -668,8 +764,20 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
     if (i32sub(effectiveTotalCore, dev->Usedcores) < k.Coresreq) { reason["CardInsufficientCore"]++; continue; }
     if (effectiveTotalCore == 100 && k.Coresreq == 100 && dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
     if (effectiveTotalCore != 0 && dev->Usedcores == effectiveTotalCore && k.Coresreq == 0) { reason["CardComputeUnitsExhausted"]++; continue; }
-    if (g.vendor == Vendor::NVIDIA && dev->Mode == "mig")
-      throw std::runtime_error("oracle: MIG devices are outside the restated scope");
+    if (g.vendor == Vendor::NVIDIA && dev->Mode == "mig") {
+      // CustomFilterRule, nvidia/device.go:602-619, with the resolved memory request (:811-814): the picks this Fit
+      // already queued on the same GPU take their placements first
+      std::vector<MigPlacement> occupied = occupiedMigPlacements(dev->MigAllocationsInUse);
+      bool ok = true;
+      MigProfile prof; MigPlacement place;
+      for (auto& existing : tmpDevs) {
+        if (existing.UUID != dev->ID) continue;
+        if (!SelectMigCandidate(dev->MigProfiles, occupied, existing.Usedmem, prof, place)) { ok = false; break; }
+        occupied.push_back(place);
+      }
+      if (ok) ok = SelectMigCandidate(dev->MigProfiles, occupied, memreq, prof, place);
+      if (!ok) { reason["CardMigTopologyInfeasible"]++; continue; }   // :819-823
+    }
     if ((g.vendor == Vendor::MTHREADS || g.vendor == Vendor::METAX) && allocated) {
       // customFilterRule, mthreads/device.go:266-276,362-366: every device an earlier container of this pod got (looked
       // up under the DEVICE's type string) must be this very device
@@ -699,6 +807,7 @@ FitResult fitTemplate(const FitGates& g, const std::vector<DeviceUsage*>& device
       FitResult r; r.fit = true; r.devs = tmpDevs;
       return r;
     }
+    if (g.vendor == Vendor::NVIDIA && dev->Mode == "mig") i++;   // nvidia/device.go:846-848: the same GPU is visited again
   }
 
   if (vastaiDie) {    // vastai/device.go:306-320; computeBestCombination :336-372 (cards with equal die counts: ascending AIC, canonical rule 7)
@@ -754,6 +863,18 @@ class NvidiaGPUDevices : public Devices {
                "nvidia.com/use-gpuuuid", "nvidia.com/nouse-gpuuuid"};
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
+  bool AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const override {   // nvidia/device.go:645-664
+    if (n.Mode == "mig") {
+      MigProfile profile; MigPlacement placement;
+      if (!SelectMigCandidate(n.MigProfiles, occupiedMigPlacements(n.MigAllocationsInUse), ctr.Usedmem, profile, placement))
+        return false;   // "MIG profile and placement allocation failed"
+      ctr.Usedmem = profile.MemoryMB;
+      ctr.Usedcores = profile.Core;
+      ctr.HasMig = true; ctr.MigProfileName = profile.Name; ctr.MigPlace = placement;
+      n.MigAllocationsInUse.push_back(MigAllocation{profile.Name, placement});
+    }
+    return Devices::AddResourceUsage(n, ctr);
+  }
   void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
     // nvidia/device.go:505-518
     auto it = pd.find("NVIDIA");
@@ -761,6 +882,8 @@ class NvidiaGPUDevices : public Devices {
       std::string s = EncodePodSingleDevice(it->second);
       annos["hami.io/vgpu-devices-to-allocate"] = s;
       annos["hami.io/vgpu-devices-allocated"] = s;
+      std::string mig = EncodeMigAllocations(it->second);
+      if (!mig.empty()) annos["hami.io/vgpu-mig-allocations"] = mig;
     }
   }
 };
@@ -935,12 +1058,13 @@ class PlainDevices : public Devices {
     if (v_.FitKind == 6) return fitNeuron(g, devices, request, pod, def);
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
-  void AddResourceUsage(DeviceUsage& n, const ContainerDevice& ctr) const override {
+  bool AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const override {
     Devices::AddResourceUsage(n, ctr);
     if (v_.FitKind == 6) {                       // awsneuron/device.go:340-355
       if (n.AwsUsage < 0) n.AwsUsage = 0;
       if (ctr.AwsUsage >= 0) n.AwsUsage += ctr.AwsUsage;
     }
+    return true;
   }
   // metax/device.go:185-214: 2000 minus the node's topology loss (binpack) / score (spread) for this many devices
   float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo) const override {
@@ -1179,6 +1303,7 @@ void Scheduler::AddNode(const NodeInfo& info) {
       u.ID = d.ID; u.Index = d.Index; u.Count = d.Count; u.Totalmem = d.Devmem; u.Totalcore = d.Devcore;
       u.Mode = d.Mode; u.Type = d.Type; u.Numa = d.Numa; u.Health = d.Health;
       u.HasNetworkID = d.HasNetworkID; u.NetworkID = d.NetworkID;
+      u.MigProfiles = d.MIGProfiles;   // scheduler.go:678
       usage.push_back(u);
     }
   }
@@ -1198,7 +1323,84 @@ void Scheduler::AddNode(const NodeInfo& info) {
     ne.alive = true;
     for (auto& kv : pods_)
       if (kv.second.NodeID == info.ID) applyUsage(ne, kv.second.Devices, +1);
+    refreshMig(ne);
   }
+}
+
+// The MIG half of getNodesUsage (scheduler.go:757-842) for one node, from scratch: which reservations are in use on
+// each device, and which devices fail closed (a MIG-mode device holding a pod without a reservation, a reservation
+// on a hami-core device, reservations left over for a non-MIG or unknown device).  The result does not depend on
+// the order the pods are visited in: reservations are consumed per pod, and Health only ever goes to false.
+void Scheduler::refreshMig(NodeEntry& ne) {
+  bool any = false;
+  for (auto& d : ne.usage) if (d.Mode == "mig") any = true;
+  if (!any)
+    for (auto& kv : pods_) if (kv.second.NodeID == ne.info.ID && !kv.second.MigAllocs.empty()) { any = true; break; }
+  if (!any && !ne.migTouched) return;
+  ne.migTouched = any;
+  size_t idx = 0;
+  for (auto& kv : ne.info.Devices)
+    for (auto& d : kv.second) {
+      if (idx < ne.usage.size()) { ne.usage[idx].Health = d.Health; ne.usage[idx].MigAllocationsInUse.clear(); }
+      idx++;
+    }
+  for (auto& pkv : pods_) {
+    const PodInfo& p = pkv.second;
+    if (p.NodeID != ne.info.ID) continue;
+    std::map<std::string, std::vector<MigReservation>> byGPU;
+    for (auto& a : p.MigAllocs) byGPU[a.GPUUUID].push_back(a);
+    for (auto& podsingleds : p.Devices)
+      for (auto& ctrdevs : podsingleds.second)
+        for (auto& udevice : ctrdevs)
+          for (auto& d : ne.usage) {
+            if (d.ID != udevice.UUID) continue;
+            auto& allocations = byGPU[udevice.UUID];
+            if (!allocations.empty()) {
+              if (d.Mode == "hami-core") { d.Health = false; continue; }          // scheduler.go:788-792
+              d.MigAllocationsInUse.push_back(MigAllocation{allocations[0].Profile, allocations[0].Placement});
+              allocations.erase(allocations.begin());
+              continue;
+            }
+            if (d.Mode == "mig") d.Health = false;                                 // :799-802, fail closed
+          }
+    for (auto& g : byGPU) {                                                        // :810-841
+      if (g.second.empty()) continue;
+      bool matched = false;
+      for (auto& d : ne.usage) {
+        if (d.ID != g.first) continue;
+        matched = true;
+        if (d.Mode != "mig") { d.Health = false; break; }
+        for (auto& a : g.second) d.MigAllocationsInUse.push_back(MigAllocation{a.Profile, a.Placement});
+        break;
+      }
+      if (!matched)
+        for (auto& d : ne.usage) if (d.Mode == "mig") d.Health = false;
+    }
+  }
+}
+
+bool Scheduler::AddPodWithMig(const std::string& uid, const std::string& ns, const std::string& node, const PodDevices& devices,
+                              const std::vector<MigReservation>& allocs) {
+  auto it = nodeIndex_.find(node);
+  if (it == nodeIndex_.end()) return false;
+  auto old = pods_.find(uid);
+  if (old != pods_.end()) {
+    auto n = nodeIndex_.find(old->second.NodeID);
+    if (n != nodeIndex_.end()) {
+      applyUsage(*nodes_[n->second], old->second.Devices, -1);
+      std::string prevNode = old->second.NodeID;
+      pods_.erase(old);
+      refreshMig(*nodes_[n->second]);
+    } else pods_.erase(old);
+  } else {
+    quota.AddUsage(ns, CountPodDevices(devices));
+  }
+  PodInfo pi;
+  pi.NodeID = node; pi.Namespace = ns; pi.Devices = devices; pi.MigAllocs = allocs;
+  pods_[uid] = pi;
+  applyUsage(*nodes_[it->second], devices, +1);
+  refreshMig(*nodes_[it->second]);
+  return true;
 }
 
 bool Scheduler::RemoveNode(const std::string& name) {
@@ -1234,6 +1436,7 @@ bool Scheduler::UsageApply(const std::string& uid, const std::string& node, cons
   if (pi.Devices["_"].empty()) pi.Devices["_"].push_back({});
   pi.Devices["_"][0].push_back(cd);
   applyUsage(*nodes_[it->second], one, +1);
+  refreshMig(*nodes_[it->second]);
   return true;
 }
 
@@ -1244,6 +1447,7 @@ bool Scheduler::DeletePod(const std::string& uid) {
   if (n != nodeIndex_.end()) applyUsage(*nodes_[n->second], it->second.Devices, -1);
   quota.RmUsage(it->second.Namespace, CountPodDevices(it->second.Devices));   // scheduler.go:250-252,1092-1094
   pods_.erase(it);
+  if (n != nodeIndex_.end()) refreshMig(*nodes_[n->second]);
   return true;
 }
 
@@ -1356,7 +1560,10 @@ bool Scheduler::FitInDevices(NodeUsage& node, const ContainerDeviceRequests& req
       DeviceUsage* d = nullptr;
       for (auto& v : node.Devices.DeviceLists) if (v.Device.ID == val.UUID) { d = &v.Device; break; }
       if (!d) { reason = "Device with UUID \"" + val.UUID + "\" not found on node " + (node.Info ? node.Info->ID : "") + " after Fit"; return false; }
-      devPlugin->AddResourceUsage(*d, val);
+      if (!devPlugin->AddResourceUsage(*d, val)) {   // score.go:125-128
+        reason = "AddResourceUsage failed for device " + d->ID + ": MIG profile and placement allocation failed";
+        return false;
+      }
     }
     devinput[k.Type].push_back(fr.devs);
   }
@@ -1544,7 +1751,8 @@ FilterResult Scheduler::Filter(const Pod& pod, const std::vector<std::string>* n
   pi.Devices = effective;
   quota.AddUsage(pod.Namespace, CountPodDevices(effective));   // scheduler.go:1136-1138
   applyUsage(*nodes_[cand[best]], effective, +1);
-  pods_[pod.UID] = pi;
+  pods_[pod.UID] = pi;      // args.Pod carries no hami.io/vgpu-mig-allocations yet: a MIG pick fails closed until the informer delivers it
+  refreshMig(*nodes_[cand[best]]);
   return fr;
 }
 

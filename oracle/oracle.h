@@ -37,8 +37,8 @@
  *  Additionally OverrideScore sums vendor ScoreNode results in sorted type-key
  *  order (policy/node_policy.go:69 ranges over a map).
  *
- * Not restated (outside the built scope, the oracle refuses such inputs):
- * dynamic MIG placement (nvidia/device.go:602-639, mig_topology.go).
+ * Dynamic MIG IS restated (nvidia/device.go:602-664,811-848, nvidia/mig_topology.go, the MIG half of getNodesUsage
+ * scheduler.go:757-842) and pinned on mig_topology_test.go, mig_capability_test.go and scheduler/mig_allocation_test.go.
  * Namespace ResourceQuota IS restated (QuotaManager / fitQuota, device/quota.go:62-150,
  * nvidia/device.go:666-692, cambricon/device.go:351-376) and pinned on TestFitQuota.
  */
@@ -55,6 +55,18 @@
 
 namespace oracle {
 
+// ---- dynamic MIG: pkg/device/devices.go:50-100 --------------------------------
+struct MigPlacement { uint32_t Start = 0, Size = 0; };            // devices.go:50-53
+struct MigProfile {                                              // devices.go:79-90
+  std::string Name;
+  int32_t MemoryMB = 0, Core = 0;
+  uint32_t SliceCount = 0;
+  std::vector<MigPlacement> Placements;
+};
+struct MigAllocation { std::string Profile; MigPlacement Placement; };   // devices.go:92-99 (the fields the path reads)
+// nvidia.MigAllocation as the hami.io/vgpu-mig-allocations annotation carries it (nvidia/mig_allocations.go:36-45)
+struct MigReservation { std::string GPUUUID, Profile; MigPlacement Placement; };
+
 // ---- pkg/device/devices.go:106-236 ------------------------------------------
 struct DeviceUsage {               // devices.go:106-125
   std::string ID;
@@ -67,6 +79,8 @@ struct DeviceUsage {               // devices.go:106-125
   bool HasNetworkID = false;       // CustomInfo["NetworkID"] present; AWSNeuron: CustomInfo["AWSNodeType"] present …
   int NetworkID = 0;               // … and 1 when that instance type contains "inf"/"Inf" (ring), else 0
   int AwsUsage = -1;               // CustomInfo["awsusageinfo"] (awsneuron/device.go:340-355,485-488), -1 = key absent
+  std::vector<MigProfile> MigProfiles;            // devices.go:116
+  std::vector<MigAllocation> MigAllocationsInUse; // devices.go:117
 };
 
 struct DeviceInfo {                // devices.go:127-144
@@ -81,6 +95,7 @@ struct DeviceInfo {                // devices.go:127-144
   bool HasNetworkID = false;
   int NetworkID = 0;
   std::map<std::string, int> PairScores;  // DevicePairScore.Scores
+  std::vector<MigProfile> MIGProfiles;    // devices.go:141
 };
 
 struct NodeInfo {                  // devices.go:170-174 (+ the node annotations Fit reads)
@@ -98,6 +113,9 @@ struct ContainerDevice {           // devices.go:205-216
   bool HasNetworkID = false;       // CustomInfo carried by the Ascend Fit (ascend/device.go:573)
   int NetworkID = 0;
   int AwsUsage = -1;               // CustomInfo["awsusageinfo"] set by the AWSNeuron Fit, -1 = absent
+  bool HasMig = false;             // CustomInfo["migProfile"] / ["migPlacement"] set by the NVIDIA AddResourceUsage (nvidia/device.go:653-657)
+  std::string MigProfileName;
+  MigPlacement MigPlace;
 };
 
 struct ContainerDeviceRequest {    // devices.go:222-228
@@ -178,7 +196,8 @@ class Devices {
                         const PodDevices* allocated = nullptr, const QuotaManager* quota = nullptr) const = 0;
   virtual ResourceNames GetResourceNames() const { return {CommonWord() + "/mem", CommonWord() + "/core", 1}; }
   virtual float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo = nullptr) const { return 0; }
-  virtual void AddResourceUsage(DeviceUsage& n, const ContainerDevice& ctr) const;
+  // returns false where the reference returns an error (only the NVIDIA MIG branch does, nvidia/device.go:646-650)
+  virtual bool AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const;
   virtual void PatchAnnotations(const Pod& pod, std::map<std::string, std::string>& annos, const PodDevices& pd) const = 0;
 };
 
@@ -202,6 +221,7 @@ struct Config {
 struct PodInfo {                   // pkg/device/pods.go:33-40
   std::string NodeID, Namespace;
   PodDevices Devices;              // collapsed
+  std::vector<MigReservation> MigAllocs;   // DecodeMigAllocations(pod.Annotations["hami.io/vgpu-mig-allocations"]), in order
 };
 
 struct FilterResult {
@@ -232,6 +252,10 @@ class Scheduler {
   bool UsageApply(const std::string& uid, const std::string& node, const std::string& uuid,
                   int32_t slots, int32_t mem, int32_t cores);
   bool DeletePod(const std::string& uid);
+  // the informer delivering a pod WITH its hami.io/vgpu-mig-allocations annotation decoded (scheduler.go:137-171 → pods.go:57-97):
+  // replaces what the cache holds for the pod
+  bool AddPodWithMig(const std::string& uid, const std::string& ns, const std::string& node, const PodDevices& devices,
+                     const std::vector<MigReservation>& allocs);
   QuotaManager quota;              // s.quotaManager
   std::map<std::string, int64_t> CountPodDevices(const PodDevices& pd) const;   // countPodDevices, quota.go:97-117
 
@@ -261,8 +285,10 @@ class Scheduler {
     NodeInfo info;
     std::vector<DeviceUsage> usage;  // lean mode: incremental usage, registration order
     bool alive = true;
+    bool migTouched = false;         // refreshMig changed Health / reservations last time: the next call must reset them
   };
   void applyUsage(NodeEntry& ne, const PodDevices& devs, int sign);
+  void refreshMig(NodeEntry& ne);   // the MIG half of getNodesUsage (scheduler.go:757-842) for one node
   void scoreRange(const std::vector<int>& cand, size_t lo, size_t hi, const Pod& pod,
                   const std::string& userNodePolicy, const DeviceScoringWeights& w,
                   std::vector<NodeScoreResult>& out) const;
@@ -289,6 +315,15 @@ bool FitQuotaForDevice(const Scheduler& s, const Pod& pod, const ContainerDevice
 PodDevices CollapseInitContainerUsage(int numInit, const PodDevices& raw);               // device/initContainer.go:36-114
 std::string EncodePodSingleDevice(const PodSingleDevice& pd);                            // devices.go:451-484
 float ComputeDefaultScore(const DeviceUsageList& devices);                               // policy/node_policy.go:106-130
+// nvidia/mig_topology.go:57-79, nvidia/device.go:621-639, mig_topology.go:85-132
+bool SelectMigPlacement(const std::vector<MigProfile>& profiles, const std::vector<MigPlacement>& occupied,
+                        const std::string& profileName, MigPlacement& out);
+bool SelectMigCandidate(const std::vector<MigProfile>& profiles, const std::vector<MigPlacement>& occupied, int32_t memory,
+                        MigProfile& profile, MigPlacement& placement);
+bool CanPlaceMigProfiles(const std::vector<MigProfile>& capabilities, const std::vector<MigPlacement>& occupied,
+                         const std::vector<std::string>& requested);
+// EncodeMigAllocations, nvidia/mig_allocations.go:48-76 ("" when there is nothing to encode)
+std::string EncodeMigAllocations(const PodSingleDevice& pd);
 
 }  // namespace oracle
 #endif

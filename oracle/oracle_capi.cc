@@ -54,6 +54,17 @@ Pod toPod(const hs_pod* p) {
   return pod;
 }
 
+std::vector<MigProfile> toMigProfiles(const hs_mig_profile* p, uint32_t n) {
+  std::vector<MigProfile> out;
+  for (uint32_t i = 0; p && i < n; i++) {
+    MigProfile m;
+    m.Name = str(p[i].name); m.MemoryMB = p[i].memory_mb; m.Core = p[i].core; m.SliceCount = p[i].slice_count;
+    for (uint32_t j = 0; j < p[i].n_placements; j++) m.Placements.push_back(MigPlacement{p[i].placements[j].start, p[i].placements[j].size});
+    out.push_back(m);
+  }
+  return out;
+}
+
 NodeInfo toNodeInfo(const hs_node_info* n) {
   NodeInfo ni;
   if (!n) return ni;
@@ -65,6 +76,7 @@ NodeInfo toNodeInfo(const hs_node_info* n) {
     di.Type = str(d.type); di.Numa = d.numa; di.Mode = str(d.mode); di.Health = d.health != 0;
     di.DeviceVendor = str(d.vendor);
     di.HasNetworkID = d.network_id >= 0; di.NetworkID = d.network_id >= 0 ? d.network_id : 0;
+    di.MIGProfiles = toMigProfiles(d.mig_profiles, d.n_mig_profiles);
     if (n->pair_scores)
       for (uint32_t j = 0; j < n->n_devices; j++)
         if (j != i) di.PairScores[str(n->devices[j].id)] = n->pair_scores[i * n->n_devices + j];
@@ -84,6 +96,9 @@ DeviceListsScore toDls(const oracle_dev& d) {
   ds.Device.Usedcores = d.usedcores; ds.Device.Mode = str(d.mode); ds.Device.Numa = d.numa; ds.Device.Type = str(d.type);
   ds.Device.Health = d.health != 0; ds.Device.HasNetworkID = d.network_id >= 0;
   ds.Device.NetworkID = d.network_id >= 0 ? d.network_id : 0;
+  ds.Device.MigProfiles = toMigProfiles(d.mig_profiles, d.n_mig_profiles);
+  for (uint32_t i = 0; d.mig_in_use && i < d.n_mig_in_use; i++)
+    ds.Device.MigAllocationsInUse.push_back(MigAllocation{"", MigPlacement{d.mig_in_use[i].start, d.mig_in_use[i].size}});
   ds.Score = d.score;
   return ds;
 }
@@ -93,11 +108,12 @@ void fillEntries(Arena& a, const PodDevices& pd) {
     const char* key = a.s(kv.first);
     for (size_t c = 0; c < kv.second.size(); c++) {
       if (kv.second[c].empty()) {
-        a.entries.push_back(hs_alloc_entry{(uint32_t)c, key, nullptr, 0, 0, 0});
+        a.entries.push_back(hs_alloc_entry{(uint32_t)c, key, nullptr, 0, 0, 0, nullptr, 0, 0});
         continue;
       }
       for (auto& cd : kv.second[c])
-        a.entries.push_back(hs_alloc_entry{(uint32_t)c, key, a.s(cd.UUID), cd.Idx, cd.Usedmem, cd.Usedcores});
+        a.entries.push_back(hs_alloc_entry{(uint32_t)c, key, a.s(cd.UUID), cd.Idx, cd.Usedmem, cd.Usedcores,
+                                           cd.HasMig ? a.s(cd.MigProfileName) : nullptr, cd.MigPlace.Start, cd.MigPlace.Size});
     }
   }
 }
@@ -164,6 +180,58 @@ int32_t oracle_node_remove(oracle_handle* o, const char* name) { return o->s->Re
 int32_t oracle_usage_apply(oracle_handle* o, const char* pod_uid, const char* node, const char* uuid,
                            int32_t slots, int32_t usedmem, int32_t usedcores) {
   return o->s->UsageApply(str(pod_uid), str(node), str(uuid), slots, usedmem, usedcores) ? HS_OK : HS_ERR_NOTFOUND;
+}
+// hs_pod_set_mig: the informer re-delivers a cached pod with its decoded reservations (pi.Pod = pod, pods.go:76-77)
+int32_t oracle_pod_set_mig(oracle_handle* o, const char* pod_uid, const hs_mig_reservation* res, uint32_t n) {
+  const PodInfo* pi = o->s->GetPod(str(pod_uid));
+  if (!pi) return HS_ERR_NOTFOUND;
+  std::vector<MigReservation> allocs;
+  for (uint32_t i = 0; i < n; i++) allocs.push_back(MigReservation{str(res[i].gpu_uuid), str(res[i].profile), MigPlacement{res[i].start, res[i].size}});
+  PodInfo copy = *pi;
+  return o->s->AddPodWithMig(str(pod_uid), copy.Namespace, copy.NodeID, copy.Devices, allocs) ? HS_OK : HS_ERR_NOTFOUND;
+}
+int32_t oracle_snapshot_node_mig(oracle_handle* o, const char* node, uint32_t* occupied, uint8_t* health, uint32_t cap) {
+  auto snap = o->s->Snapshot(str(node));
+  uint32_t n = 0;
+  for (auto& d : snap) {
+    if (n < cap) {
+      uint32_t m = 0;
+      for (auto& a : d.MigAllocationsInUse) for (uint32_t b = a.Placement.Start; b < a.Placement.Start + a.Placement.Size && b < 32; b++) m |= 1u << b;
+      if (occupied) occupied[n] = m;
+      if (health) health[n] = d.Health ? 1 : 0;
+    }
+    n++;
+  }
+  return (int32_t)n;
+}
+/* test hooks: nvidia/mig_topology.go selectMigPlacement / canPlaceMigProfiles and nvidia/device.go selectMigCandidate */
+int32_t oracle_mig_select_placement(const hs_mig_profile* profiles, uint32_t n, const hs_mig_placement* occupied, uint32_t n_occ,
+                                    const char* profile, hs_mig_placement* out) {
+  std::vector<MigPlacement> occ;
+  for (uint32_t i = 0; i < n_occ; i++) occ.push_back(MigPlacement{occupied[i].start, occupied[i].size});
+  MigPlacement pl;
+  if (!SelectMigPlacement(toMigProfiles(profiles, n), occ, str(profile), pl)) return 0;
+  if (out) { out->start = pl.Start; out->size = pl.Size; }
+  return 1;
+}
+int32_t oracle_mig_can_place(const hs_mig_profile* profiles, uint32_t n, const hs_mig_placement* occupied, uint32_t n_occ,
+                             const char* const* requested, uint32_t n_req) {
+  std::vector<MigPlacement> occ;
+  for (uint32_t i = 0; i < n_occ; i++) occ.push_back(MigPlacement{occupied[i].start, occupied[i].size});
+  std::vector<std::string> req;
+  for (uint32_t i = 0; i < n_req; i++) req.push_back(str(requested[i]));
+  return CanPlaceMigProfiles(toMigProfiles(profiles, n), occ, req) ? 1 : 0;
+}
+int32_t oracle_mig_select_candidate(const hs_mig_profile* profiles, uint32_t n, const hs_mig_placement* occupied, uint32_t n_occ,
+                                    int32_t memory, int32_t* profile_index, hs_mig_placement* out) {
+  std::vector<MigPlacement> occ;
+  for (uint32_t i = 0; i < n_occ; i++) occ.push_back(MigPlacement{occupied[i].start, occupied[i].size});
+  auto ps = toMigProfiles(profiles, n);
+  MigProfile pr; MigPlacement pl;
+  if (!SelectMigCandidate(ps, occ, memory, pr, pl)) return 0;
+  if (profile_index) { *profile_index = -1; for (uint32_t i = 0; i < n; i++) if (ps[i].Name == pr.Name) { *profile_index = (int32_t)i; break; } }
+  if (out) { out->start = pl.Start; out->size = pl.Size; }
+  return 1;
 }
 int32_t oracle_pod_delete(oracle_handle* o, const char* pod_uid) { return o->s->DeletePod(str(pod_uid)) ? HS_OK : HS_ERR_NOTFOUND; }
 
@@ -383,7 +451,7 @@ int32_t oracle_fit(oracle_handle* o, const char* vendor_key, const oracle_dev* d
     FitResult fr = v->Fit(ptrs, k, p, node_info ? &ni : nullptr, o->s->config().GPUSchedulerPolicy);
     out->status = fr.fit ? HS_FIT : HS_NOFIT;
     const char* key = a.s(k.Type);
-    for (auto& cd : fr.devs) a.entries.push_back(hs_alloc_entry{0, key, a.s(cd.UUID), cd.Idx, cd.Usedmem, cd.Usedcores});
+    for (auto& cd : fr.devs) a.entries.push_back(hs_alloc_entry{0, key, a.s(cd.UUID), cd.Idx, cd.Usedmem, cd.Usedcores, nullptr, 0, 0});
     a.failed.push_back(hs_failed_node{a.s(""), a.s(fr.reason)});
     finish(a, out);
     return fr.fit ? 1 : 0;
@@ -479,7 +547,7 @@ int32_t oracle_collapse(const hs_alloc_entry* in, uint32_t n_in, uint32_t n_init
   for (auto& kv : c)
     for (auto& cds : kv.second)
       for (auto& cd : cds) {
-        if (n < cap) out[n] = hs_alloc_entry{0, a.s(kv.first), a.s(cd.UUID), cd.Slots, cd.Usedmem, cd.Usedcores};
+        if (n < cap) out[n] = hs_alloc_entry{0, a.s(kv.first), a.s(cd.UUID), cd.Slots, cd.Usedmem, cd.Usedcores, nullptr, 0, 0};
         n++;
       }
   return (int32_t)n;

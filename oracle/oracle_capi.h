@@ -27,6 +27,10 @@ typedef struct oracle_dev {
   uint8_t     health;
   int32_t     network_id; /* -1 absent */
   float       score;
+  const hs_mig_profile*   mig_profiles;   /* DeviceUsage.MigProfiles */
+  uint32_t                n_mig_profiles;
+  const hs_mig_placement* mig_in_use;     /* placements of DeviceUsage.MigAllocationsInUse */
+  uint32_t                n_mig_in_use;
 } oracle_dev;
 
 oracle_handle* oracle_create(const hs_config* cfg);
@@ -38,6 +42,15 @@ int32_t oracle_node_remove(oracle_handle* o, const char* name);
 int32_t oracle_usage_apply(oracle_handle* o, const char* pod_uid, const char* node, const char* uuid,
                            int32_t slots, int32_t usedmem, int32_t usedcores);
 int32_t oracle_pod_delete(oracle_handle* o, const char* pod_uid);
+/* dynamic MIG: the informer side and the state getNodesUsage derives (see hs_pod_set_mig / hs_snapshot_node_mig) */
+int32_t oracle_pod_set_mig(oracle_handle* o, const char* pod_uid, const hs_mig_reservation* res, uint32_t n);
+int32_t oracle_snapshot_node_mig(oracle_handle* o, const char* node, uint32_t* occupied, uint8_t* health, uint32_t cap);
+int32_t oracle_mig_select_placement(const hs_mig_profile* profiles, uint32_t n, const hs_mig_placement* occupied, uint32_t n_occ,
+                                    const char* profile, hs_mig_placement* out);
+int32_t oracle_mig_can_place(const hs_mig_profile* profiles, uint32_t n, const hs_mig_placement* occupied, uint32_t n_occ,
+                             const char* const* requested, uint32_t n_req);
+int32_t oracle_mig_select_candidate(const hs_mig_profile* profiles, uint32_t n, const hs_mig_placement* occupied, uint32_t n_occ,
+                                    int32_t memory, int32_t* profile_index, hs_mig_placement* out);
 /* podManager.GetPod (pods.go:146-155): node and collapsed per-device usage of one cached pod, summed per UUID;
  * returns the number of rows or HS_ERR_NOTFOUND.  Strings are valid until the next call. */
 int32_t oracle_pod_get(oracle_handle* o, const char* pod_uid, const char** node_name, hs_pod_usage_row* rows, uint32_t cap);

@@ -18,7 +18,9 @@ class oracle_dev(C.Structure):
     _fields_ = [("id", C.c_char_p), ("index", C.c_uint32), ("used", C.c_int32), ("count", C.c_int32),
                 ("usedmem", C.c_int32), ("totalmem", C.c_int32), ("totalcore", C.c_int32), ("usedcores", C.c_int32),
                 ("mode", C.c_char_p), ("numa", C.c_int32), ("type", C.c_char_p), ("health", C.c_uint8),
-                ("network_id", C.c_int32), ("score", C.c_float)]
+                ("network_id", C.c_int32), ("score", C.c_float),
+                ("mig_profiles", C.POINTER(abi.hs_mig_profile)), ("n_mig_profiles", C.c_uint32),
+                ("mig_in_use", C.POINTER(abi.hs_mig_placement)), ("n_mig_in_use", C.c_uint32)]
 
 
 _lib = None
@@ -69,12 +71,42 @@ def lib():
     L.oracle_parse_weights.argtypes = [C.c_char_p, P(C.c_int64)]
     L.oracle_gen_reason.argtypes = [P(C.c_int32), C.c_int32, C.c_char_p, C.c_size_t]
     L.oracle_collapse.argtypes = [P(abi.hs_alloc_entry), C.c_uint32, C.c_uint32, P(abi.hs_alloc_entry), C.c_uint32]
+    L.oracle_pod_set_mig.argtypes = [C.c_void_p, C.c_char_p, P(abi.hs_mig_reservation), C.c_uint32]
+    L.oracle_snapshot_node_mig.argtypes = [C.c_void_p, C.c_char_p, P(C.c_uint32), P(C.c_uint8), C.c_uint32]
+    L.oracle_mig_select_placement.argtypes = [P(abi.hs_mig_profile), C.c_uint32, P(abi.hs_mig_placement), C.c_uint32,
+                                              C.c_char_p, P(abi.hs_mig_placement)]
+    L.oracle_mig_can_place.argtypes = [P(abi.hs_mig_profile), C.c_uint32, P(abi.hs_mig_placement), C.c_uint32,
+                                       P(C.c_char_p), C.c_uint32]
+    L.oracle_mig_select_candidate.argtypes = [P(abi.hs_mig_profile), C.c_uint32, P(abi.hs_mig_placement), C.c_uint32,
+                                              C.c_int32, P(C.c_int32), P(abi.hs_mig_placement)]
     _lib = L
     return L
 
 
+_mig_keep = []   # ctypes arrays the oracle_dev rows point into (fixtures are tiny; kept for the life of the process)
+
+
+def mig_profiles_from_go(profiles):
+    """Go []device.MigProfile literal -> the dicts abi.build_mig_profiles takes"""
+    return [{"name": p.get("Name", ""), "memory_mb": int(p.get("MemoryMB", 0)), "core": int(p.get("Core", 0)),
+             "slice_count": int(p.get("SliceCount", 0)),
+             "placements": [(int(q.get("Start", 0)), int(q.get("Size", 0))) for q in (p.get("Placements") or [])]}
+            for p in (profiles or [])]
+
+
+def placements_array(pl):
+    arr = (abi.hs_mig_placement * max(1, len(pl)))()
+    for i, (st, sz) in enumerate(pl):
+        arr[i] = abi.hs_mig_placement(st, sz)
+    return arr
+
+
 def dev_from_go(d, score=0.0):
     """Go DeviceUsage literal (fixture dict with Go field names) -> oracle_dev"""
+    mp, nmp = abi.build_mig_profiles(mig_profiles_from_go(d.get("MigProfiles")), _mig_keep)
+    inuse = [(int(a["Placement"].get("Start", 0)), int(a["Placement"].get("Size", 0))) for a in (d.get("MigAllocationsInUse") or [])]
+    iu = placements_array(inuse) if inuse else None
+    _mig_keep.append(iu)
     net = -1
     ci = d.get("CustomInfo")
     if isinstance(ci, dict) and "NetworkID" in ci:
@@ -86,7 +118,8 @@ def dev_from_go(d, score=0.0):
     return oracle_dev(abi._b(d.get("ID", "")), int(d.get("Index", 0)), int(d.get("Used", 0)), int(d.get("Count", 0)),
                       int(d.get("Usedmem", 0)), int(d.get("Totalmem", 0)), int(d.get("Totalcore", 0)),
                       int(d.get("Usedcores", 0)), abi._b(d.get("Mode", "")), int(d.get("Numa", 0)),
-                      abi._b(d.get("Type", "")), 1 if d.get("Health", False) else 0, net, float(score))
+                      abi._b(d.get("Type", "")), 1 if d.get("Health", False) else 0, net, float(score),
+                      mp, nmp, iu, len(inuse))
 
 
 def devs_array(devs):
@@ -132,6 +165,17 @@ class Oracle:
 
     def pod_delete(self, uid):
         return self.L.oracle_pod_delete(self.h, abi._b(uid))
+
+    def pod_set_mig(self, uid, reservations):
+        keep = []
+        arr, n = abi.build_mig_reservations(reservations, keep)
+        return self.L.oracle_pod_set_mig(self.h, abi._b(uid), arr, n)
+
+    def snapshot_node_mig(self, node, cap=16):
+        occ = (C.c_uint32 * cap)()
+        hl = (C.c_uint8 * cap)()
+        n = self.L.oracle_snapshot_node_mig(self.h, abi._b(node), occ, hl, cap)
+        return [(occ[i], hl[i]) for i in range(max(0, n))]
 
     def pod_get(self, uid):
         rows = (abi.hs_pod_usage_row * 16)()

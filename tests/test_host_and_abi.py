@@ -44,7 +44,9 @@ def test_no_cpu_fallback():
 def test_struct_sizes_match_header():
     # guards the ctypes mirror against drifting from include/hami_sched.h
     assert C.sizeof(abi.hs_container_request) == 32
-    assert C.sizeof(abi.hs_alloc_entry) == 40
+    assert C.sizeof(abi.hs_alloc_entry) == 56      # + mig_profile / mig_start / mig_size
+    assert C.sizeof(abi.hs_mig_profile) == 40 and C.sizeof(abi.hs_mig_placement) == 8
+    assert C.sizeof(abi.hs_device_info) == 88
     assert C.sizeof(abi.hs_kv) == 16
     assert C.sizeof(abi.hs_device_usage_row) == 12
 

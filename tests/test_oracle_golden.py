@@ -253,8 +253,6 @@ def _fit_table(orc, case, vendor, type_fix=None, annos_fix=None):
 @pytest.mark.parametrize("case", load("nvidia_fit"), ids=ids(load("nvidia_fit")))
 def test_nvidia_fit(orc, case):
     # nvidia/device_test.go:753-1224
-    if _has_mig(case["devices"]):
-        pytest.skip("dynamic MIG is outside the restated scope (SURVEY §8f N3)")
     _fit_table(orc, case, "NVIDIA")
 
 
@@ -313,8 +311,6 @@ def test_ascend_fit_910c(orc, case):
 def test_fit_in_certain_device(orc, case):
     # score_test.go:3291-3829: nvidia Fit over getNodeResources(node, "NVIDIA") with reason histograms
     devices = [go_device(dl["Device"]) for dl in case["args"]["node"]["Devices"]["DeviceLists"]]
-    if _has_mig(devices):
-        pytest.skip("dynamic MIG is outside the restated scope (SURVEY §8f N3)")
     devices = [d for d in devices if "nvidia" in d.get("Type", "").lower()]  # getNodeResources, score.go:43-52
     pod = case["args"].get("pod") or {}
     annos = ((pod.get("ObjectMeta") or {}).get("Annotations")) if isinstance(pod, dict) else {}
@@ -380,8 +376,6 @@ def test_calc_score(orc, case):
     for node_id, nu in args["nodes"].items():
         dl = nu["Devices"]
         devs = [oa.dev_from_go(go_device(x["Device"]), x.get("Score", 0)) for x in dl.get("DeviceLists") or []]
-        if any(d.mode == b"mig" for d in devs):
-            pytest.skip("dynamic MIG is outside the restated scope (SURVEY §8f N3)")
         p, keep = abi.build_pod(pod)
         res = abi.hs_filter_result()
         rc = orc.L.oracle_score_node(orc.h, abi._b(node_id), oa.devs_array(devs), len(devs),
