@@ -516,6 +516,10 @@ typedef struct hs_mig_reservation {
   uint32_t    start, size;
 } hs_mig_reservation;
 int32_t hs_pod_set_mig(hs_handle* h, const char* pod_uid, const hs_mig_reservation* res, uint32_t n);
+/* nvidia.DecodeMigAllocations (nvidia/mig_allocations.go:78-112) on its own: pure host code, output in thread-local
+ * storage until the next hs_decode_* call on this thread; HS_ERR_INVALID with the reason in hs_last_error(NULL) for
+ * malformed JSON, an incomplete entry, a partial runtime identity or a duplicate (containerIndex, deviceIndex).    */
+int32_t hs_decode_mig_allocations(const char* json, const hs_mig_reservation** out, uint32_t* n);
 /* What getNodesUsage would hand Fit for one node's MIG state: per device the occupied-slice mask (bit s = slice s
  * is covered by a reservation in use) and whether the device is healthy after the fail-closed rules.  Rows in the
  * node's device order; returns the number of devices.                                                           */

@@ -17,7 +17,7 @@ _lib = None
 EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_run_batch_async", "hs_batch_wait", "hs_batch_get", "hs_rollback",
-    "hs_snapshot_node", "hs_pod_get", "hs_pod_set_mig", "hs_snapshot_node_mig", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
+    "hs_snapshot_node", "hs_pod_get", "hs_pod_set_mig", "hs_snapshot_node_mig", "hs_decode_mig_allocations", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
     "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect",
     "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_filter_dry", "hs_filter_simulate", "hs_quota_set", "hs_quota_del", "hs_quota_get", "hs_quota_memory_factor", "hs_generate_requests", "hs_debug_timing", "hs_debug_window_stats", "hs_debug_decision_ns", "hs_debug_copy_bytes", "hs_debug_host_seconds", "hs_debug_divcheck", "hs_debug_metax_table",
 ]
@@ -117,7 +117,25 @@ def decode_node_devices(vendor, fmt, annotation, pair_scores=None, node_name=Non
             "Devcore": devs[i].devcore, "Type": devs[i].type.decode(), "Numa": devs[i].numa, "Mode": devs[i].mode.decode(),
             "Health": bool(devs[i].health), "DeviceVendor": devs[i].vendor.decode(), "NetworkID": devs[i].network_id}
            for i in range(n.value)]
+    for i in range(n.value):      # DeviceInfo.MIGProfiles, present for GPUs that report any
+        if devs[i].n_mig_profiles:
+            out[i]["MigProfiles"] = [
+                {"name": p.name.decode(), "memory_mb": p.memory_mb, "core": p.core, "slice_count": p.slice_count,
+                 "placements": [(p.placements[j].start, p.placements[j].size) for j in range(p.n_placements)]}
+                for p in (devs[i].mig_profiles[k] for k in range(devs[i].n_mig_profiles))]
     return out, ([pair[i] for i in range(n.value * n.value)] if pair else None)
+
+
+def decode_mig_allocations(raw):
+    """hs_decode_mig_allocations (host only): [(gpu_uuid, profile, start, size)]; IngestError where the reference's
+    DecodeMigAllocations returns an error."""
+    L = lib()
+    out, n = C.POINTER(abi.hs_mig_reservation)(), C.c_uint32()
+    L.hs_decode_mig_allocations.argtypes = [C.c_char_p, C.POINTER(C.POINTER(abi.hs_mig_reservation)), C.POINTER(C.c_uint32)]
+    rc = L.hs_decode_mig_allocations(abi._b(raw), C.byref(out), C.byref(n))
+    if rc != 0:
+        raise IngestError(rc, L.hs_last_error(None).decode())
+    return [(out[i].gpu_uuid.decode(), out[i].profile.decode(), out[i].start, out[i].size) for i in range(n.value)]
 
 
 def _pod_devices_out(devs, n):

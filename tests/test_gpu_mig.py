@@ -219,3 +219,43 @@ def test_mig_stream_parity(seed, node_policy, gpu_policy):
     assert n_mig_picks > 40 and n_fit > 100 and n_nofit > 5, (n_mig_picks, n_fit, n_nofit)
     e.close()
     o.close()
+
+
+def test_register_annotation_and_pod_annotations_carry_mig_state():
+    # the reference-facing ingest path: hs_node_register decodes DeviceInfo.migProfiles from hami.io/node-nvidia-register
+    # (devices.go:127-144), a Filter's own annotations come back through hs_pod_ingest the way onAddPod sees the patched
+    # pod (scheduler.go:137-171) — against an oracle fed the same facts directly
+    import k8s_vgpu_scheduler_b200.engine as eng
+    from oracle_abi import abi
+    e, o = both()
+    reg = json.dumps([
+        {"id": "GPU-0", "count": 7, "devmem": 40960, "devcore": 100, "type": "NVIDIA-A100", "numa": 0, "health": True, "mode": "mig",
+         "migProfiles": [{"name": p["name"], "memoryMB": p["memory_mb"], "core": p["core"], "sliceCount": p["slice_count"],
+                          "placements": [{"start": s, "size": z} for s, z in p["placements"]]} for p in A100]},
+        {"id": "GPU-1", "index": 1, "count": 10, "devmem": 40960, "devcore": 100, "type": "NVIDIA-A100", "numa": 0, "health": True, "mode": "hami-core"},
+    ])
+    assert e.node_register("node1", [("NVIDIA", abi.HS_REG_JSON, reg, None)]) == 2
+    node = {"name": "node1", "devices": [gpu("GPU-0", 0, "mig", A100), gpu("GPU-1", 1, "hami-core")]}
+    o.node_upsert(node)
+    seq = [pod("a", 9000, 2, {"nvidia.com/vgpu-mode": "mig"}), pod("b", 3000, 1, {"nvidia.com/vgpu-mode": "mig"}),
+           pod("c", 18000, 1, {"nvidia.com/vgpu-mode": "mig"}), pod("d", 18000, 1, {"nvidia.com/vgpu-mode": "mig"})]
+    for p in seq:
+        r, g = o.filter(p), e.filter(p)
+        assert parity.compare([("filter", p)], [r], [g]) == [], p["uid"]
+        same_state(e, o, [node])
+        if g["status"] != 0:
+            continue
+        # the informer: the patched pod comes back with the annotations Filter returned
+        annos = dict(g["annotations"])
+        annos["hami.io/vgpu-node"] = "node1"
+        assert e.pod_ingest(p["uid"], "node1", annos) == 0
+        assert o.pod_set_mig(p["uid"], reservations_of(r)) == 0
+        same_state(e, o, [node])
+    occ, healthy = e.snapshot_node_mig("node1")[0]
+    assert healthy == 1 and occ != 0
+    # a mangled annotation decodes to no reservation: the GPU fails closed again (scheduler.go:760-766,799-802)
+    annos = {"hami.io/vgpu-devices-allocated": "GPU-0,NVIDIA,10240,28:;", "hami.io/vgpu-mig-allocations": "[{broken"}
+    assert e.pod_ingest("a", "node1", annos) == 0
+    assert e.snapshot_node_mig("node1")[0][1] == 0
+    e.close()
+    o.close()

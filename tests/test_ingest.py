@@ -399,3 +399,39 @@ def test_pod_decoder_and_collapse_match_oracle_on_random_input():
         for mode in (0, 1):
             assert with_slots(OracleImpl.collapse(mode, n_init, a)) == with_slots(ProductImpl.collapse(mode, n_init, a)), (mode, n_init, annos)
     assert 50 < errs < 1500
+
+
+# ---- dynamic MIG: what the register annotation and the pod annotation carry ------------------------------------
+def test_mig_profiles_from_the_register_annotation():
+    # nvidia/device_test.go:2466-2482 (TestGetNodeDevices_MigProfilesFromNode): name and placements survive the decode
+    c = [x for x in gold("ingest_funcs")["nvidia_get_node_devices"] if x["name"] == "TestGetNodeDevices_MigProfilesFromNode"][0]
+    devs, _ = eng.decode_node_devices("NVIDIA", abi.HS_REG_JSON, c["register"])
+    assert len(devs) == 1 and devs[0]["Mode"] == "mig"
+    assert devs[0]["MigProfiles"] == [{"name": "1g.5gb", "memory_mb": 5120, "core": 14, "slice_count": 1, "placements": [(6, 1)]}]
+
+
+def test_decode_mig_allocations_golden():
+    # nvidia/mig_profiles_test.go:36-88
+    one = '[{"containerIndex":0,"deviceIndex":0,"gpuUUID":"GPU-a","profile":"1g.5gb","placement":{"start":6,"size":1}}]'
+    assert eng.decode_mig_allocations(one) == [("GPU-a", "1g.5gb", 6, 1)]                       # TestEncodeDecodeMigAllocations
+    assert eng.decode_mig_allocations("") == []
+    dup = ('[{"containerIndex":0,"deviceIndex":0,"gpuUUID":"GPU-a","profile":"1g.5gb","placement":{"start":6,"size":1}},'
+           '{"containerIndex":0,"deviceIndex":0,"gpuUUID":"GPU-a","profile":"1g.5gb","placement":{"start":5,"size":1}}]')
+    with pytest.raises(eng.IngestError, match="duplicate MIG allocation for container 0 device 0"):  # …RejectsDuplicateDeviceIndex
+        eng.decode_mig_allocations(dup)
+    full = ('[{"containerIndex":0,"deviceIndex":0,"gpuUUID":"GPU-a","profile":"2g.10gb","placement":{"start":0,"size":2},'
+            '"migUUID":"MIG-a","gpuInstanceID":4,"computeInstanceID":0}]')
+    assert eng.decode_mig_allocations(full) == [("GPU-a", "2g.10gb", 0, 2)]                      # …PreservesZeroRuntimeInstanceIDs
+    part = '[{"containerIndex":0,"deviceIndex":0,"gpuUUID":"GPU-a","profile":"2g.10gb","placement":{"start":0,"size":2},"migUUID":"MIG-a"}]'
+    with pytest.raises(eng.IngestError, match="partial runtime identity"):                       # …RejectsPartialRuntimeIdentity
+        eng.decode_mig_allocations(part)
+    with pytest.raises(eng.IngestError, match="MIG allocation 0 is incomplete"):
+        eng.decode_mig_allocations('[{"containerIndex":0,"deviceIndex":0,"gpuUUID":"GPU-a","profile":"1g.5gb","placement":{"start":6,"size":0}}]')
+    with pytest.raises(eng.IngestError):
+        eng.decode_mig_allocations("not json")
+    # the scheduler's own test annotation, two reservations on one GPU (scheduler/mig_allocation_test.go:96-99)
+    two = '''[
+        {"containerIndex":0,"deviceIndex":0,"gpuUUID":"GPU-a","profile":"1g.5gb","placement":{"start":6,"size":1}},
+        {"containerIndex":0,"deviceIndex":1,"gpuUUID":"GPU-a","profile":"1g.5gb","placement":{"start":5,"size":1}}
+    ]'''
+    assert eng.decode_mig_allocations(two) == [("GPU-a", "1g.5gb", 6, 1), ("GPU-a", "1g.5gb", 5, 1)]
