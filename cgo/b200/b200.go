@@ -31,6 +31,7 @@ import (
 	corev1 "k8s.io/api/core/v1"
 
 	"github.com/Project-HAMi/HAMi/pkg/device"
+	"github.com/Project-HAMi/HAMi/pkg/device/nvidia"
 	"github.com/Project-HAMi/HAMi/pkg/scheduler/policy"
 )
 
@@ -210,6 +211,26 @@ func (e *Engine) UpsertNode(info *device.NodeInfo, cordon string, hasCordon bool
 		if len(d.DevicePairScore.Scores) > 0 {
 			anyPair = true
 		}
+		if d.Mode == "mig" && len(d.MIGProfiles) > 0 { // DeviceInfo.MIGProfiles, devices.go:141: what dynamic MIG selects from
+			profs := (*[1 << 8]C.hs_mig_profile)(a.alloc(uintptr(len(d.MIGProfiles)), unsafe.Sizeof(C.hs_mig_profile{})))
+			for k, mp := range d.MIGProfiles {
+				profs[k].name = a.str(mp.Name)
+				profs[k].memory_mb = C.int32_t(mp.MemoryMB)
+				profs[k].core = C.int32_t(mp.Core)
+				profs[k].slice_count = C.uint32_t(mp.SliceCount)
+				if len(mp.Placements) > 0 {
+					pl := (*[1 << 8]C.hs_mig_placement)(a.alloc(uintptr(len(mp.Placements)), unsafe.Sizeof(C.hs_mig_placement{})))
+					for q, p := range mp.Placements {
+						pl[q].start = C.uint32_t(p.Start)
+						pl[q].size = C.uint32_t(p.Size)
+					}
+					profs[k].placements = &pl[0]
+					profs[k].n_placements = C.uint32_t(len(mp.Placements))
+				}
+			}
+			arr[i].mig_profiles = &profs[0]
+			arr[i].n_mig_profiles = C.uint32_t(len(d.MIGProfiles))
+		}
 	}
 	var ni C.hs_node_info
 	ni.name = a.str(info.ID)
@@ -274,6 +295,34 @@ func (e *Engine) AddPod(uid, node string, devices device.PodDevices) error {
 				}
 			}
 		}
+	}
+	return nil
+}
+
+// SetPodMigAllocations hands the engine the decoded hami.io/vgpu-mig-allocations annotation of a cached pod
+// (nvidia.DecodeMigAllocations; read by getNodesUsage, scheduler.go:757-842).  Call it from onAddPod / onUpdatePod
+// after AddPod: a GPU in MIG mode that Filter just picked stays unhealthy until its pod's reservation arrives here,
+// as in the reference, where Filter caches the unpatched pod (scheduler.go:1132-1139).  A decode error in the caller
+// counts as no reservation: pass nil.
+func (e *Engine) SetPodMigAllocations(uid string, allocations []nvidia.MigAllocation) error {
+	var a arena
+	defer a.free()
+	cu := a.str(uid)
+	var first *C.hs_mig_reservation
+	if len(allocations) > 0 {
+		arr := (*[1 << 10]C.hs_mig_reservation)(a.alloc(uintptr(len(allocations)), unsafe.Sizeof(C.hs_mig_reservation{})))
+		for i, al := range allocations {
+			arr[i].gpu_uuid = a.str(al.GPUUUID)
+			arr[i].profile = a.str(al.Profile)
+			arr[i].start = C.uint32_t(al.Placement.Start)
+			arr[i].size = C.uint32_t(al.Placement.Size)
+		}
+		first = &arr[0]
+	}
+	e.mu.Lock()
+	defer e.mu.Unlock()
+	if rc := C.hs_pod_set_mig(e.h, cu, first, C.uint32_t(len(allocations))); rc != C.HS_OK && rc != C.HS_ERR_NOTFOUND {
+		return e.lastError(rc)
 	}
 	return nil
 }
@@ -367,8 +416,15 @@ func readResult(res *C.hs_filter_result, nContainers int) *Result {
 			single = append(single, device.ContainerDevices{})
 		}
 		if en.uuid != nil { // uuid == NULL marks an empty ContainerDevices at that position (score.go:266-282 padding)
-			single[en.container] = append(single[en.container], device.ContainerDevice{
-				Idx: int(en.idx), UUID: C.GoString(en.uuid), Type: key, Usedmem: int32(en.usedmem), Usedcores: int32(en.usedcores)})
+			cd := device.ContainerDevice{
+				Idx: int(en.idx), UUID: C.GoString(en.uuid), Type: key, Usedmem: int32(en.usedmem), Usedcores: int32(en.usedcores)}
+			if en.mig_profile != nil { // the reservation AddResourceUsage made on a GPU in MIG mode (nvidia/device.go:653-657)
+				cd.CustomInfo = map[string]any{
+					nvidia.MigProfileCustomInfo:   C.GoString(en.mig_profile),
+					nvidia.MigPlacementCustomInfo: device.MigPlacement{Start: uint32(en.mig_start), Size: uint32(en.mig_size)},
+				}
+			}
+			single[en.container] = append(single[en.container], cd)
 		}
 		devs[key] = single
 	}

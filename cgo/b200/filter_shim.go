@@ -63,7 +63,7 @@ func Filter(e *Engine, g GoPath, args extenderv1.ExtenderArgs) (*extenderv1.Exte
 		g.QuotaRm(args.Pod, old)
 	}
 	res, err := e.Filter(args.Pod, reqs, names)
-	if errors.Is(err, ErrUnsupported) { // dynamic MIG, > 8 devices on a node, a vendor the engine does not hold
+	if errors.Is(err, ErrUnsupported) { // > 8 devices on a node, a vendor the engine does not hold, a topology-aware pod beside MIG GPUs
 		return g.FilterGo(args)
 	}
 	if err != nil { // scheduler.go:1096-1107
