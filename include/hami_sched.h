@@ -274,7 +274,18 @@ enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
         * exactly `nums`, the first one when nums == 1, else cards by die count (descending; equal counts in ascending
         * AIC, canonical rule 7), dies inside a card in walk order (:306-320,336-372); ScoreNode = largest share of one
         * card among a container's dies, unweighted (:181-216).  A node must be all-die or all-card.                  */
-       HS_FIT_VASTAI = 7 };
+       HS_FIT_VASTAI = 7,
+       /* kunlun whole XPUs (pkg/device/kunlun/device.go:184-240, kunlun/topo.go).  Fit = graghSelect over the node's
+        * kunlun devices in LIST order: positions 0-3 are the left wing, 4-7 the right; a device fits when it is idle and
+        * healthy and passes BOTH uuid annotation pairs (hami.io/use-xpu-uuid / no-use-xpu-uuid and
+        * baidu.com/use-gpuuuid / nouse-gpuuuid).  8 cards: all of them; 1, 2 or 4: the wing whose free count is the
+        * tightest match (1 → 1,3,2,4; 2 → 2,3,4; 4 → 4), else an inter-group pair (2) or interconnect group (4) by card
+        * Index; anything else does not fit.  Failure: the number of cards a uuid list turned away, else "1/n NumaNotFit".
+        * The picks take the whole card (Totalmem, Totalcore) but AddResourceUsage only counts the slot (:179-182).
+        * ScoreNode (:154-177): 0 unless every device of the node is a kunlun card, else 3000 / 2000 / 1000 / 0 by how
+        * the "bubble" count of half-used wings changes (calcscore, topo.go:74-95).  Annotations: the allocated key and
+        * BAIDU_COM_DEVICE_IDX = the card indices of the last container with devices (:93-110).  Card Index < 32.       */
+       HS_FIT_KUNLUN = 8 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */
@@ -409,7 +420,7 @@ typedef struct hs_container_resources {
 } hs_container_resources;
 enum { HS_REQ_NVIDIA = 0, HS_REQ_DCU = 1, HS_REQ_MLU = 2, HS_REQ_ASCEND = 3,
        HS_REQ_ILUVATAR = 4,   /* iluvatar/device.go:201-254: memory_factor 256, cores default 0                  */
-       HS_REQ_COUNT = 5,      /* biren/device.go:141-165, vastai/device.go:143-167: the count only               */
+       HS_REQ_COUNT = 5,      /* biren/device.go:141-165, vastai/device.go:143-167, kunlun/device.go:129-152: the count only */
        HS_REQ_AMD = 6,        /* amd/device.go:217-266: Limits only; cores = percent of the card, default 100     */
        HS_REQ_MTHREADS = 7,   /* mthreads/device.go:202-264: memory_factor 512; memory and cores divided by count */
        HS_REQ_WHOLE_CARD = 8, /* enflame/gcu.go:91-111: Memreq 100, MemPercentagereq 100, Coresreq 100            */
@@ -445,6 +456,8 @@ enum { HS_REG_CSV = 0,    /* device.DecodeNodeDevices  (pkg/device/devices.go:31
        HS_REG_CAPACITY_METAX = 4,    /* metax/device.go:67-89: capacity_cores = the GPU count, <node>-metax-<i>, Count 1;
                                       * `annotation` / `pair_scores` = the node's metax-tech.com/gpu.topology.losses /
                                       * .scores values or NULL (hs_node_register hands them to hs_node_info)            */
+       HS_REG_CAPACITY_KUNLUN = 6,   /* kunlun/device.go:64-91: capacity_cores = the XPU count, <node>-kunlun-<i>, Count 100,
+                                      * 98304 MiB, the upper half of the cards on NUMA 1                                */
        HS_REG_CAPACITY_NEURON = 5    /* awsneuron/device.go:156-198: capacity_cores = the DEVICE count, capacity_memory = the
                                       * node's total core count, capacity_aux = the vendor object's coresPerAWSNeuron so far
                                       * (0 = unknown: total / count, which the caller then keeps), `annotation` = the node's

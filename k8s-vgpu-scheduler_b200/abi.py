@@ -87,6 +87,7 @@ class hs_sim_node(C.Structure):
 
 
 HS_REG_CSV, HS_REG_JSON, HS_REG_CAPACITY_MLU, HS_REG_CAPACITY_MTHREADS, HS_REG_CAPACITY_METAX, HS_REG_CAPACITY_NEURON = 0, 1, 2, 3, 4, 5
+HS_REG_CAPACITY_KUNLUN = 6
 
 
 class hs_container_request(C.Structure):
@@ -167,6 +168,7 @@ class hs_vendor_config(C.Structure):
 
 
 HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD, HS_FIT_METAX, HS_FIT_NEURON, HS_FIT_VASTAI = 0, 1, 2, 3, 4, 5, 6, 7
+HS_FIT_KUNLUN = 8
 
 # The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
 # (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
@@ -191,6 +193,8 @@ DEFAULT_VENDORS = [
     # awsneuron/device.go:42-58,68-79 (SupportDevices only: no to-allocate key is written)
     ("AWSNeuron", HS_FIT_NEURON, "aws.amazon.com/use-neuron-uuid", "aws.amazon.com/nouse-neuron-uuid", None,
      "hami.io/aws-neuron-devices-allocated"),
+    # kunlun whole XPUs (kunlun/device.go:32-56): SupportDevices only; the second uuid pair (baidu.com/...) is fixed in the Fit
+    ("kunlun", HS_FIT_KUNLUN, "hami.io/use-xpu-uuid", "hami.io/no-use-xpu-uuid", None, "hami.io/kunlun-allocated"),
 ]
 
 

@@ -143,6 +143,8 @@ struct NodeSlot {
   std::string cordon;
   int vnpu = -1;
   std::vector<std::string> base_types;  // nodeDeviceBaseTypes, score.go:71-79 (sorted, unique)
+  std::vector<std::string> vendor_base_types;   // the base types that are themselves a registered vendor word: their
+                                                // PatchAnnotations sees a (padded) entry under its key even when the pod asked for none
   bool has_mig = false;        // some device is in MIG mode
   bool mig_touched = false;    // the last mig_refresh left MIG bookkeeping in the node's dflags
 };
@@ -161,6 +163,7 @@ struct VendorInfo {
   bool metax = false;       // metax whole GPUs: mthreads' gates without uuid lists + ScoreNode from the node's annotations (EF_METAX)
   int fit_kind = 0;         // HS_FIT_* as registered (hs_filter_simulate hands it on to the child handle)
   bool vastai = false;      // vastai: count-only gates + die mode (EF_VASTAI)
+  bool kunlun = false;      // kunlun whole XPUs: graghSelect, slot-only usage, wing ScoreNode (EF_KUNLUN)
   bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
 };
@@ -707,6 +710,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       if (v && v->metax) e.flags |= EF_METAX;
       if (v && v->neuron) e.flags |= EF_NEURON;
       if (v && v->whole_card) e.flags |= EF_WHOLE_CARD;
+      if (v && v->kunlun) e.flags |= EF_KUNLUN;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
       if (v && v->ascend910) e.flags |= EF_ASCEND910;
@@ -720,7 +724,32 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
           e.has_use = 1;
           if (!uuid_words(h, list, uuid_pool, e.use_off, e.use_cnt)) { h->err = "use-uuid list spans too many nodes"; return HS_ERR_UNSUPPORTED; }
         }
-        if (get_anno(pod, v->nouse_uuid, list) && !trimSpace(list).empty())
+        std::string use2, nouse2;
+        if (v->kunlun) {
+          // kunlun's fitFn consults a second, fixed pair as well (kunlun/device.go:196-201): a card must pass both, so the
+          // use lists intersect and the no-use lists unite
+          if (get_anno(pod, "baidu.com/use-gpuuuid", use2) && !trimSpace(use2).empty()) {
+            if (e.has_use) {
+              std::set<std::string> a;
+              for (auto& u : splitComma(list)) a.insert(trimSpace(u));
+              std::string both;
+              for (auto& u : splitComma(use2)) if (a.count(trimSpace(u))) { if (!both.empty()) both += ","; both += trimSpace(u); }
+              if (both.empty()) both = "\x01";       // no card passes both lists (no UUID is this string)
+              use2 = both;
+            }
+            e.has_use = 1;
+            e.use_off = 0; e.use_cnt = 0;
+            if (!uuid_words(h, use2, uuid_pool, e.use_off, e.use_cnt)) { h->err = "use-uuid list spans too many nodes"; return HS_ERR_UNSUPPORTED; }
+          }
+          if (get_anno(pod, "baidu.com/nouse-gpuuuid", nouse2) && !trimSpace(nouse2).empty()) {
+            std::string first;
+            if (get_anno(pod, v->nouse_uuid, first) && !trimSpace(first).empty()) nouse2 = first + "," + nouse2;
+            e.nouse_off = 0; e.nouse_cnt = 0;
+            if (!uuid_words(h, nouse2, uuid_pool, e.nouse_off, e.nouse_cnt)) { h->err = "no-use-uuid list spans too many nodes"; return HS_ERR_UNSUPPORTED; }
+            nouse2 = "\x02";
+          }
+        }
+        if (nouse2 != "\x02" && get_anno(pod, v->nouse_uuid, list) && !trimSpace(list).empty())
           if (!uuid_words(h, list, uuid_pool, e.nouse_off, e.nouse_cnt)) { h->err = "no-use-uuid list spans too many nodes"; return HS_ERR_UNSUPPORTED; }
       }
       keyset.insert(ktype);
@@ -749,7 +778,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     // pairing stays with the general evaluator
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
               !(e.flags & EF_ASCEND910C)) ? 1 : 0;
-    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX | EF_NEURON))) p.fast = 0;
+    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX | EF_NEURON | EF_KUNLUN))) p.fast = 0;
   }
   if (h->has_mig)       // dynamic MIG lives in the general evaluator: every NVIDIA request of a handle that holds a GPU in MIG mode
     for (const DevEntry& e : c.entries) {
@@ -1310,7 +1339,8 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
     // request's type key holding the rows, plus one empty list under every other base type of the node
     // (score.go:278-282), and the annotation map to four keys.  Same output as the general code, no maps.
     if (m.n_ctr == 1 && m.n_init == 0 && m.entries.size() == 1 && (m.entries[0].vendor == 0 || m.entries[0].vendor == 1) &&
-        h->b_entries.h[h->b_pods.h[op].entry_off].nums > 0 && !ns.has_mig) {
+        h->b_entries.h[h->b_pods.h[op].entry_off].nums > 0 && !ns.has_mig &&
+        (ns.vendor_base_types.empty() || (ns.vendor_base_types.size() == 1 && ns.vendor_base_types[0] == m.entries[0].type))) {
       const EntryMeta& em = m.entries[0];
       const VendorInfo& v = h->vendors[em.vendor];
       bool placed = false;
@@ -1443,6 +1473,15 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
           annos["mthreads.com/gpu-index"] = value;
           annos["mthreads.com/predicate-time"] = "";
           annos["mthreads.com/predicate-node"] = ns.name;
+        }
+        continue;
+      }
+      if (v.kunlun) {     // kunlun/device.go:93-110: the allocated key; the card indices of the LAST container with devices
+        annos[v.allocated] = s;
+        for (auto& ctr : it->second) {
+          std::string value;
+          for (auto* e : ctr) { if (!value.empty()) value += ","; value += std::to_string(e->idx); }
+          if (!value.empty()) annos["BAIDU_COM_DEVICE_IDX"] = value;
         }
         continue;
       }
@@ -2184,6 +2223,7 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.whole_card = vc.fit_kind == HS_FIT_WHOLE_CARD;
       v.metax = vc.fit_kind == HS_FIT_METAX;
       v.neuron = vc.fit_kind == HS_FIT_NEURON;
+      v.kunlun = vc.fit_kind == HS_FIT_KUNLUN;
       if (v.metax) { v.use_uuid.clear(); v.nouse_uuid.clear(); }   // checkUUID is constant true (metax/device.go:124-126)
       if (vc.use_type_key) v.use_type = vc.use_type_key;
       if (vc.nouse_type_key) v.nouse_type = vc.nouse_type_key;
@@ -2276,6 +2316,9 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
     if (s.mode_id < 0) { h->err = "more distinct device modes than supported"; return HS_ERR_UNSUPPORTED; }
     auto v = h->vendor_by_word.find(s.vendor);
     s.vendor_id = v == h->vendor_by_word.end() ? HV_NONE : v->second;
+    if (s.vendor_id != HV_NONE && h->vendors[s.vendor_id].kunlun && (s.index > 31 || s.devcore > 32767 || s.devcore < -32768)) {
+      h->err = "kunlun card outside the engine's range (Index < 32, Devcore in int16)"; return HS_ERR_UNSUPPORTED;
+    }
     if (s.vendor_id != HV_NONE && h->vendors[s.vendor_id].neuron && (s.devcore > 32767 || s.devcore < 0)) {
       h->err = "AWS Neuron core mask outside the engine's int16 allocation row"; return HS_ERR_UNSUPPORTED;
     }
@@ -2371,6 +2414,8 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
   std::set<std::string> bt;
   for (auto& d : ns.devs) bt.insert(d.type);
   ns.base_types.assign(bt.begin(), bt.end());
+  ns.vendor_base_types.clear();
+  for (auto& t : ns.base_types) if (h->vendor_by_word.count(t)) ns.vendor_base_types.push_back(t);
   std::set<std::string> cordoned;  // cordonedDevices, nvidia/device.go:698-713
   if (ns.has_cordon && !trimSpace(ns.cordon).empty())
     for (auto& u0 : splitComma(ns.cordon)) { std::string u = trimSpace(u0); if (!u.empty()) cordoned.insert(u); }
@@ -2431,6 +2476,11 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
   if (ns.vnpu >= 0) vnpu = ns.vnpu == 1;
   if (vnpu) nf |= NF_VNPU_CORE;
   for (const auto& d : ns.devs) { if (d.type == "NVIDIA") nf |= NF_BASE_NV; if (d.type == "MLU") nf |= NF_BASE_MLU; }
+  {   // kunlun ScoreNode returns 0 as soon as one device of the node is not a kunlun card (kunlun/device.go:157-160)
+    bool all = !ns.devs.empty();
+    for (const auto& d : ns.devs) if (d.type.find("kunlun") == std::string::npos) all = false;
+    if (all) nf |= NF_ALL_KUNLUN;
+  }
   h->h_flags[slot] = nf;
   {
     h->h_tot[slot] = make_int4((int)nf, host_node_score_bits(h, slot), 0, 0);

@@ -19,6 +19,7 @@ struct NodeWork {
   float score[HS_D];                                 // DeviceListsScore.Score
   uint32_t order;                                    // nibble i = device slot at list position i
   uint32_t mth_prev;                                 // EF_MTHREADS: device slots the pod's earlier containers (of this phase) received
+  uint32_t kl_cur;                                   // EF_KUNLUN: card indices the pod received so far, all containers (ScoreNode's `current`)
   int aws[HS_D];                                     // EF_NEURON: CustomInfo["awsusageinfo"] of the working copy, -1 = key absent
   int ndev;
 };
@@ -244,6 +245,85 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
     for (int r = 0; r < 16; r++) out.reasons[r] = 0;
     out.fkind = FK_HIST;
     out.fcards = (uint32_t)cnt;
+  }
+  if (e.flags & EF_KUNLUN) {
+    // kunlun whole XPUs: graghSelect (kunlun/topo.go:206-252) over the typeDevices in LIST order; fitFn = both uuid pairs
+    // (merged into one use / no-use list on the host) and FitXPU = idle and healthy (device.go:196-206,238-240)
+    uint32_t useMaskK = 0xffu, nouseMaskK = 0u;
+    if (e.has_use) useMaskK = uuid_mask_lookup(ka.uuid_pool, e.use_off, e.use_cnt, node);
+    if (e.nouse_cnt) nouseMaskK = uuid_mask_lookup(ka.uuid_pool, e.nouse_off, e.nouse_cnt, node);
+    uint32_t fit = 0;              // by list position
+    int idx[HS_D];
+    int mism = 0, left = 0, right = 0;
+    for (int i = 0; i < cnt; i++) {
+      const int d = td[i];
+      idx[i] = (int)PK_INDEX(w.packed[d]);
+      const bool uu = ((useMaskK >> d) & 1u) && !((nouseMaskK >> d) & 1u);
+      if (!uu) { mism++; continue; }
+      if (w.used[d] == 0 && (w.dflags[d] & DF_HEALTH)) { fit |= 1u << i; if (i < 4) left++; else right++; }
+    }
+    const int count = e.nums;
+    int alloc[HS_D], na = 0;
+    if (count == 8) {
+      if (left + right == 8) for (int i = 0; i < 8; i++) alloc[na++] = i;
+    } else if (count == 1 || count == 2 || count == 4) {
+      int start = -1;
+      if (left >= count || right >= count)
+        for (int slots = count; slots <= 4 && start < 0; slots++) {
+          const int num = (count & 1) ? (slots == 1 ? 1 : slots == 2 ? 3 : slots == 3 ? 2 : 4) : slots;     // oddorder {1,3,2,4}
+          if (left == num) start = 0;
+          else if (right == num) start = 4;
+        }
+      if (start >= 0) {                                           // devicepick, :192-204
+        for (int t = start; t < 8 && t < cnt && na < count; t++) if ((fit >> t) & 1u) alloc[na++] = idx[t];
+      } else if (count == 2) {                                    // interconnect, :112-131: the first inter-group pair in walk order
+        for (int a = 0; a < cnt && na == 0; a++) {
+          if (!((fit >> a) & 1u)) continue;
+          for (int b = 0; b < cnt && na == 0; b++) {
+            if (!((fit >> b) & 1u) || idx[b] == idx[a]) continue;
+            const int lo = idx[a] < idx[b] ? idx[a] : idx[b], hi = idx[a] < idx[b] ? idx[b] : idx[a];
+            if (lo < 4 && hi == lo + 4) { alloc[0] = idx[a]; alloc[1] = idx[b]; na = 2; }
+          }
+        }
+      } else if (count == 4) {                                    // :132-160
+        uint32_t unused = 0;
+        int nun = 0;
+        for (int i = 0; i < cnt; i++) if ((fit >> i) & 1u) { nun++; if (idx[i] < 32) unused |= 1u << idx[i]; }
+        const uint32_t inter2[6] = {0x33u, 0xccu, 0x55u, 0xaau, 0x99u, 0x66u};   // 0-1-4-5, 2-3-6-7, 0-2-4-6, 1-3-5-7, 0-3-4-7, 1-2-5-6
+        const uint32_t order[6][4] = {{0, 1, 4, 5}, {2, 3, 6, 7}, {0, 2, 4, 6}, {1, 3, 5, 7}, {0, 3, 4, 7}, {1, 2, 5, 6}};
+        int chosen = -1;
+        if (nun == 4 || nun == 5) {
+          for (int c = 0; c < 6 && chosen < 0; c++) if ((unused & inter2[c]) == inter2[c]) chosen = c;
+        } else if (nun == 6) {
+          for (int c = 0; c < 6; c++) {
+            if ((unused & inter2[c]) != inter2[c]) continue;
+            chosen = c;
+            const uint32_t rest = unused & ~inter2[c];             // delta: two cards; connected = an inter-group or in-group pair
+            bool connected = false;
+            for (int a = 0; a < 8; a++)
+              for (int b = a + 1; b < 8; b++)
+                if (((rest >> a) & 1u) && ((rest >> b) & 1u) && (b == a + 4 || (a < 4) == (b < 4))) connected = true;
+            if (connected) break;
+          }
+        }
+        if (chosen >= 0) for (int i = 0; i < 4; i++) alloc[na++] = (int)order[chosen][i];
+      }
+    }
+    if (na == 0) {
+      if (MODE == EV_EXPLAIN) { if (mism > 0) out.reasons[1] += (uint32_t)mism; else out.reasons[8]++; }
+      return false;
+    }
+    for (int a = 0; a < na; a++)
+      for (int i = 0; i < cnt; i++) {
+        const int d = td[i];
+        if ((int)PK_INDEX(w.packed[d]) != alloc[a]) continue;
+        fc.tmp_dev[fc.ntmp] = d;
+        fc.tmp_mem[fc.ntmp] = w.totmem[d];
+        fc.tmp_cores[fc.ntmp] = w.totcore[d];
+        fc.ntmp++;
+        break;
+      }
+    return true;
   }
   if (e.flags & EF_NEURON) {
     // AWS Neuron, awsneuron/device.go:443-541.  Totalcore / Usedcores are core bit masks; w.aws is the working copy's
@@ -611,9 +691,16 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
         if (w.aws[d] < 0) w.aws[d] = 0;
         w.aws[d] += fc.tmp_aws[t];
       }
-      w.used[d] += 1;
-      w.cores[d] += pick_cores;
-      w.mem[d] += fc.tmp_mem[t];
+      if (e.flags & EF_KUNLUN) {          // kunlun/device.go:179-182: AddResourceUsage counts the slot only; the pick keeps the whole card
+        pick_cores = fc.tmp_cores[t];
+        w.used[d] += 1;
+        const int ki = (int)PK_INDEX(w.packed[d]);
+        if (ki < 32) w.kl_cur |= 1u << ki;
+      } else {
+        w.used[d] += 1;
+        w.cores[d] += pick_cores;
+        w.mem[d] += fc.tmp_mem[t];
+      }
       if (MODE == EV_RECORD && out.n_alloc < HS_MAX_ALLOC) {
         DevAlloc a;
         a.entry = (uint8_t)(ei);
@@ -659,6 +746,12 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   if (ka.quota != nullptr && (pod.q_idx[0] >= 0 || pod.q_idx[1] >= 0)) { quota_load(qacc, pod, ka); qa = &qacc; }
   const bool base_key[2] = {(nflags & NF_BASE_NV) != 0, (nflags & NF_BASE_MLU) != 0};
   w.mth_prev = 0;
+  w.kl_cur = 0;
+  uint32_t kl_prev = 0;               // kunlun ScoreNode's `previous`: cards in use before the pod (score.SnapshotDevice, score.go:328)
+  bool has_kunlun = false;
+  for (int e = 0; e < pod.n_entries; e++) if (ent[e].flags & EF_KUNLUN) has_kunlun = true;
+  if (has_kunlun)
+    for (int d = 0; d < w.ndev; d++) if (w.used[d] > 0 && PK_INDEX(w.packed[d]) < 32) kl_prev |= 1u << PK_INDEX(w.packed[d]);
   uint32_t metax_slots = 0;           // score slots that belong to a metax type (their accumulator is a device count)
   uint32_t plain_slots = 0;           // … to a vastai type: ScoreNode is the plain sum, no weight (vastai/device.go:181-216)
   for (int e = 0; e < pod.n_entries; e++) {
@@ -715,6 +808,20 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
       else if ((pod.flags & PF_NODE_SPREAD) && (nflags & NF_METAX_SCORE)) v = __fsub_rn(2000.0f, (float)(cnt < 32 ? (int)T[32 + cnt] : 0));
     }
     devScore = __fadd_rn(devScore, v);
+  }
+  if (has_kunlun && (nflags & NF_ALL_KUNLUN)) {
+    // kunlun ScoreNode (device.go:154-177) + calcscore / countbubble (topo.go:50-95).  It is the only non-zero term on such
+    // a node (every device is a kunlun card), so its place in the sum does not matter.
+    int bubble[2];
+    const uint32_t sets[2] = {kl_prev, w.kl_cur};
+    for (int k = 0; k < 2; k++) {
+      const int left = __popc(sets[k] & 0xfu), right = __popc(sets[k] >> 4);
+      const int gl = left == 4 ? 0 : (left == 1 ? 2 : 1), gr = right == 4 ? 0 : (right == 1 ? 2 : 1);
+      bubble[k] = (left == 0 && right == 0) ? 1 : gl + gr;
+    }
+    const int diff = bubble[1] - bubble[0];
+    const float ks = diff == -1 ? 3000.0f : (diff == 0 ? 2000.0f : (diff == 2 ? 0.0f : 1000.0f));
+    devScore = __fadd_rn(devScore, ks);
   }
   *score_out = __fadd_rn(pre, devScore);
   return true;

@@ -500,6 +500,19 @@ bool neuron_devices_from_capacity(const std::string& node, int64_t counts, int64
 // ---- vendors without a register annotation: devices derived from the node's capacity -----------------------
 bool devices_from_capacity(int kind, const std::string& node, int64_t cores, int64_t memory, std::vector<Device>& out, std::string& err) {
   out.clear();
+  if (kind == 3) {                                         // kunlun/device.go:64-91: `cores` carries the XPU count; the upper half sits on NUMA 1
+    if (cores == 0) { err = "device not found kunlunxin.com/xpu"; return false; }
+    for (int64_t i = 0; i < cores; i++) {
+      Device d;
+      d.index = (uint32_t)i;
+      d.id = node + "-kunlun-" + std::to_string(i);
+      d.count = 100; d.devmem = 98304; d.devcore = 100; d.type = "kunlun"; d.health = true;
+      d.numa = i >= cores / 2 ? 1 : 0;
+      out.push_back(d);
+      if (out.size() > 4096) { err = "capacity yields more than 4096 cards"; out.clear(); return false; }
+    }
+    return true;
+  }
   if (kind == 2) {                                         // metax/device.go:67-89: `cores` carries the GPU count
     if (cores == 0) { err = "device not found metax-tech.com/gpu"; return false; }
     for (int64_t i = 0; i < cores; i++) {

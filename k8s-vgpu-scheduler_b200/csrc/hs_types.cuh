@@ -48,6 +48,7 @@
 #define NF_BASE_NV 128u     // some device of the node has Type == "NVIDIA" exactly: the key pads like a base type (score.go:71-79,246-250)
 #define NF_BASE_MLU 256u    // … Type == "MLU"
 #define NF_METAX_LOSS 512u  // the node has metax-tech.com/gpu.topology.losses: pair[0..31] = value for that many devices
+#define NF_ALL_KUNLUN 2048u // every device of the node has a Type containing "kunlun" (kunlun ScoreNode returns 0 otherwise, device.go:157-160)
 #define NF_METAX_SCORE 1024u // … gpu.topology.scores: pair[32..63]  (metax/device.go:185-214)
 
 // vendor predicate ids (device-side switch, one code path, no dispatch layer)
@@ -67,6 +68,7 @@ enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
 #define EF_MTHREADS 32u    // mthreads' Fit (mthreads/device.go:289-405): template gates + customFilterRule (one card per pod)
 #define EF_AMD 16u         // amd's Fit (amd/device.go:279-371): whole-card memory by default, cores as a share of the card
 #define EF_VASTAI 512u     // vastai: EF_COUNT_ONLY gates; on a node of dies (NetworkID = AIC) card exclusivity under mutex, pick by card, ScoreNode
+#define EF_KUNLUN 1024u    // kunlun whole XPUs (kunlun/device.go:184-240, topo.go): graghSelect over list positions, slot-only usage, ScoreNode by wings
 #define EF_COUNT_ONLY 8u   // biren's Fit (biren/device.go:190-248): gates end after mutex; the pick has Usedmem 0, Usedcores = Coresreq
 
 struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 64 B

@@ -360,6 +360,95 @@ bool Devices::AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const {
   return true;
 }
 
+// ---- kunlun/topo.go -----------------------------------------------------------------------------
+static bool klCanMeet(const std::vector<int>& have, const std::vector<int>& want) {       // :163-175
+  for (int v : want) if (std::find(have.begin(), have.end(), v) == have.end()) return false;
+  return true;
+}
+static std::vector<int> klDevicePick(const std::vector<bool>& fit, const std::vector<int>& index, int start, int count) {   // :192-204
+  std::vector<int> res;
+  for (int t = start; t < 8; t++) {
+    if (t >= (int)fit.size()) throw std::runtime_error("kunlun devicepick past the end of the device list (the reference panics)");
+    if (fit[t]) { res.push_back(index[t]); if ((int)res.size() == count) return res; }
+  }
+  return res;
+}
+static std::vector<int> klInterconnect(const std::vector<bool>& fit, const std::vector<int>& index, int count) {   // :112-161
+  static const int inter[4][2] = {{0, 4}, {1, 5}, {2, 6}, {3, 7}};                             // InterGroupConnection
+  static const int inter2[6][4] = {{0, 1, 4, 5}, {2, 3, 6, 7}, {0, 2, 4, 6}, {1, 3, 5, 7}, {0, 3, 4, 7}, {1, 2, 5, 6}};   // InterGroupConnection2
+  static const int group[12][2] = {{0, 1}, {0, 2}, {0, 3}, {1, 2}, {1, 3}, {2, 3}, {4, 5}, {4, 6}, {4, 7}, {5, 6}, {5, 7}, {6, 7}};   // GroupConnection
+  const size_t n = fit.size();
+  if (count == 2) {
+    for (size_t a = 0; a < n; a++) {
+      if (!fit[a]) continue;
+      for (size_t b = 0; b < n; b++) {
+        if (!fit[b] || index[b] == index[a]) continue;
+        for (auto& p : inter)
+          if ((p[0] == index[a] && p[1] == index[b]) || (p[0] == index[b] && p[1] == index[a])) return {index[a], index[b]};
+      }
+    }
+  }
+  if (count == 4) {
+    std::vector<int> unused;                                                                    // parseUsage, :30-38
+    for (size_t i = 0; i < n; i++) if (fit[i]) unused.push_back(index[i]);
+    if (unused.size() == 4 || unused.size() == 5)
+      for (auto& c : inter2) { std::vector<int> cv(c, c + 4); if (klCanMeet(unused, cv)) return cv; }
+    if (unused.size() == 6) {
+      std::vector<int> ret;
+      for (auto& c : inter2) {
+        std::vector<int> cv(c, c + 4);
+        if (!klCanMeet(unused, cv)) continue;
+        ret = cv;
+        std::vector<int> d;                                                                     // delta, :177-190
+        for (int v : unused) if (std::find(cv.begin(), cv.end(), v) == cv.end()) d.push_back(v);
+        for (auto& p : inter) if (klCanMeet(d, {p[0], p[1]})) return ret;                       // parseInterconnection: inter-group pairs, then in-group pairs
+        for (auto& p : group) if (klCanMeet(d, {p[0], p[1]})) return ret;
+      }
+      return ret;
+    }
+  }
+  return {};
+}
+std::vector<int> KunlunGraphSelect(const std::vector<bool>& fit, const std::vector<int>& index, int count) {   // :206-252
+  int leftwing = 0, rightwing = 0;
+  for (size_t idx = 0; idx < fit.size(); idx++) {
+    if (idx < 4) { if (fit[idx]) leftwing++; }
+    else if (fit[idx]) rightwing++;
+  }
+  static const int oddorder[4] = {1, 3, 2, 4};
+  if (count == 8) {
+    if (leftwing + rightwing == count) return {0, 1, 2, 3, 4, 5, 6, 7};
+    return {};
+  }
+  if (count == 1 || count == 2 || count == 4) {
+    if (leftwing >= count || rightwing >= count)
+      for (int slots = count; slots <= 4; slots++) {
+        int num = slots;
+        if (count % 2 == 1) num = oddorder[slots - 1];
+        if (leftwing == num) return klDevicePick(fit, index, 0, count);
+        if (rightwing == num) return klDevicePick(fit, index, 4, count);
+      }
+    return klInterconnect(fit, index, count);
+  }
+  return {};
+}
+float KunlunCalcScore(const std::vector<int>& p, const std::vector<int>& c) {                   // :74-95 (the sorts compare positions: no-ops)
+  auto getvalue = [](int t) { return t == 4 ? 0 : (t == 1 ? 2 : 1); };                          // :50-58
+  auto countbubble = [&](const std::vector<int>& t) {                                           // :60-72
+    int left = 0, right = 0;
+    for (int v : t) { if (v < 4) left++; else right++; }
+    if (left == 0 && right == 0) return 1;
+    return getvalue(left) + getvalue(right);
+  };
+  switch (countbubble(c) - countbubble(p)) {
+    case -1: return 3000;
+    case 0: return 2000;
+    case 1: return 1000;
+    case 2: return 0;
+  }
+  return 1000;
+}
+
 // ---- dynamic MIG: nvidia/mig_topology.go ---------------------------------------------------
 static bool migPlacementsOverlap(const MigPlacement& a, const MigPlacement& b) {   // mig_topology.go:78-80
   return (uint64_t)a.Start < (uint64_t)b.Start + b.Size && (uint64_t)b.Start < (uint64_t)a.Start + a.Size;
@@ -1042,6 +1131,46 @@ FitResult fitNeuron(const FitGates& g, const std::vector<DeviceUsage*>& devices,
   return r;
 }
 
+// ---- kunlun (whole XPUs): kunlun/topo.go + kunlun/device.go:184-231 ---------------------------------------------
+// Fit runs graghSelect over the typeDevices in LIST order (wings = positions 0-3 / 4-7), FitXPU = idle and healthy,
+// the two use/no-use uuid annotation pairs applied inside fitFn; a failure reads the number of devices a uuid list
+// turned away, else one NumaNotFit.
+FitResult fitKunlun(const std::string& word, const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod) {
+  std::set<std::string> uuidMismatches;
+  std::vector<bool> fit;
+  std::vector<int> index;
+  for (auto d : devices) {
+    bool ok;
+    if (!CheckUUID(pod.Annotations, d->ID, "hami.io/use-xpu-uuid", "hami.io/no-use-xpu-uuid") ||
+        !CheckUUID(pod.Annotations, d->ID, "baidu.com/use-gpuuuid", "baidu.com/nouse-gpuuuid")) {
+      uuidMismatches.insert(d->ID);
+      ok = false;
+    } else ok = d->Used == 0 && d->Health;            // FitXPU, :238-240
+    fit.push_back(ok);
+    index.push_back((int)d->Index);
+  }
+  std::vector<int> alloc = KunlunGraphSelect(fit, index, (int)request.Nums);
+  FitResult r;
+  if (alloc.empty()) {
+    std::map<std::string, int> reason;
+    if (!uuidMismatches.empty()) reason["CardUuidMismatch"] += (int)uuidMismatches.size();
+    else reason["NumaNotFit"]++;
+    r.fit = false; r.reason = GenReason(reason, (int)devices.size());
+    return r;
+  }
+  for (int dev : alloc)
+    for (auto val : devices)
+      if (val->Index == (unsigned)dev) {
+        ContainerDevice cd;
+        cd.Idx = (int)val->Index; cd.UUID = val->ID; cd.Type = request.Type; cd.Usedmem = val->Totalmem; cd.Usedcores = val->Totalcore;
+        r.devs.push_back(cd);
+        break;
+      }
+  r.fit = true;
+  (void)word;
+  return r;
+}
+
 // iluvatar (one instance per CommonWord, iluvatar/device.go:60-83) and biren (biren/device.go:54-66)
 class PlainDevices : public Devices {
  public:
@@ -1052,6 +1181,7 @@ class PlainDevices : public Devices {
                 const QuotaManager* quota) const override {
     static const Vendor kinds[] = {Vendor::PLAIN, Vendor::COUNT_ONLY, Vendor::AMD, Vendor::MTHREADS, Vendor::WHOLE_CARD, Vendor::METAX,
                                    Vendor::PLAIN /* 6 = Neuron, below */, Vendor::VASTAI};
+    if (v_.FitKind == 8) return fitKunlun(v_.CommonWord, devices, request, pod);
     FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 7 ? v_.FitKind : 0],
                v_.CommonWord,
                v_.UseType, v_.NoUseType, v_.UseUUID, v_.NoUseUUID};
@@ -1059,6 +1189,7 @@ class PlainDevices : public Devices {
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
   bool AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const override {
+    if (v_.FitKind == 8) { n.Used = i32add(n.Used, 1); return true; }      // kunlun/device.go:179-182: the slot only
     Devices::AddResourceUsage(n, ctr);
     if (v_.FitKind == 6) {                       // awsneuron/device.go:340-355
       if (n.AwsUsage < 0) n.AwsUsage = 0;
@@ -1067,7 +1198,23 @@ class PlainDevices : public Devices {
     return true;
   }
   // metax/device.go:185-214: 2000 minus the node's topology loss (binpack) / score (spread) for this many devices
-  float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo) const override {
+  float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo,
+                  const std::vector<DeviceUsage>* previous) const override {
+    if (v_.FitKind == 8) {            // kunlun/device.go:154-177
+      std::vector<int> current, prev;
+      auto addidx = [](std::vector<int>& t, int v) { if (std::find(t.begin(), t.end(), v) == t.end()) t.push_back(v); };
+      if (previous)
+        for (auto& d : *previous) {
+          if (!Contains(d.Type, "kunlun")) return 0;
+          if (d.Used > 0) addidx(prev, (int)d.Index);
+        }
+      for (auto& ctr : podDevices)
+        for (auto& val : ctr) {
+          if (!Contains(val.Type, "kunlun")) return 0;
+          addidx(current, val.Idx);
+        }
+      return KunlunCalcScore(prev, current);
+    }
     if (v_.FitKind == 7) {            // vastai/device.go:181-216: largest share of one card among a container's dies, unweighted
       float score = 0;
       for (auto& containerDevices : podDevices) {
@@ -1118,6 +1265,17 @@ class PlainDevices : public Devices {
           annos["mthreads.com/gpu-index"] = value;
           annos["mthreads.com/predicate-time"] = "";
           annos["mthreads.com/predicate-node"] = annos["hami.io/vgpu-node"];
+        }
+        return;
+      }
+      if (v_.FitKind == 8) {
+        // kunlun/device.go:93-110: the allocated key only, and BAIDU_COM_DEVICE_IDX = the card indices of the LAST
+        // container that received devices
+        annos[v_.Allocated] = s;
+        for (auto& dp : it->second) {
+          std::string value;
+          for (auto& d : dp) { if (!value.empty()) value += ","; value += std::to_string(d.Idx); }
+          if (!value.empty()) annos["BAIDU_COM_DEVICE_IDX"] = value;
         }
         return;
       }
@@ -1196,7 +1354,7 @@ class AscendDevices : public Devices {
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
   // ascend/device.go:388-424
-  float ScoreNode(const PodSingleDevice& podDevices, const std::string&, const NodeInfo*) const override {
+  float ScoreNode(const PodSingleDevice& podDevices, const std::string&, const NodeInfo*, const std::vector<DeviceUsage>*) const override {
     if (!HasPrefix(cfg_.CommonWord, "Ascend910")) return 0;
     float score = 0;
     for (auto& containerDevices : podDevices) {
@@ -1602,6 +1760,8 @@ NodeScoreResult Scheduler::ScoreNode(const std::string& nodeID, NodeUsage& node,
   NodeScore score;
   score.NodeID = nodeID;
   score.Score = ComputeDefaultScore(appNodeCopy.Devices);
+  std::vector<DeviceUsage> snapshot;        // score.SnapshotDevice, score.go:328
+  for (auto& dl : appNodeCopy.Devices.DeviceLists) snapshot.push_back(dl.Device);
 
   int appIndex = 0;
   for (int ctrid = 0; ctrid < (int)pod.Reqs.size(); ctrid++) {
@@ -1635,7 +1795,7 @@ NodeScoreResult Scheduler::ScoreNode(const std::string& nodeID, NodeUsage& node,
   for (auto& kv : score.Devices) {
     const Devices* dev = Vendor(kv.first);
     if (!dev) continue;
-    devScore = devScore + dev->ScoreNode(kv.second, userNodePolicy, node.Info);
+    devScore = devScore + dev->ScoreNode(kv.second, userNodePolicy, node.Info, &snapshot);
   }
   score.Score = score.Score + devScore;
   res.fit = true;

@@ -195,7 +195,9 @@ class Devices {
                         const Pod& pod, const NodeInfo* nodeInfo, const std::string& gpuPolicyDefault,
                         const PodDevices* allocated = nullptr, const QuotaManager* quota = nullptr) const = 0;
   virtual ResourceNames GetResourceNames() const { return {CommonWord() + "/mem", CommonWord() + "/core", 1}; }
-  virtual float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo = nullptr) const { return 0; }
+  // previous = score.SnapshotDevice(appNodeCopy.Devices): every device of the node before the app containers are placed (score.go:328)
+  virtual float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo = nullptr,
+                          const std::vector<DeviceUsage>* previous = nullptr) const { return 0; }
   // returns false where the reference returns an error (only the NVIDIA MIG branch does, nvidia/device.go:646-650)
   virtual bool AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const;
   virtual void PatchAnnotations(const Pod& pod, std::map<std::string, std::string>& annos, const PodDevices& pd) const = 0;
@@ -316,6 +318,10 @@ PodDevices CollapseInitContainerUsage(int numInit, const PodDevices& raw);      
 std::string EncodePodSingleDevice(const PodSingleDevice& pd);                            // devices.go:451-484
 float ComputeDefaultScore(const DeviceUsageList& devices);                               // policy/node_policy.go:106-130
 // nvidia/mig_topology.go:57-79, nvidia/device.go:621-639, mig_topology.go:85-132
+// kunlun/topo.go: graghSelect over list positions (fit[i] = fitFn of the device at position i, index[i] = its Index),
+// calcscore on the card indices in use before / picked now
+std::vector<int> KunlunGraphSelect(const std::vector<bool>& fit, const std::vector<int>& index, int count);
+float KunlunCalcScore(const std::vector<int>& prev, const std::vector<int>& cur);
 bool SelectMigPlacement(const std::vector<MigProfile>& profiles, const std::vector<MigPlacement>& occupied,
                         const std::string& profileName, MigPlacement& out);
 bool SelectMigCandidate(const std::vector<MigProfile>& profiles, const std::vector<MigPlacement>& occupied, int32_t memory,

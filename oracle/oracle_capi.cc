@@ -4,6 +4,7 @@
 #include <array>
 #include <chrono>
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
 #include <deque>
 #include <stdexcept>
@@ -232,6 +233,14 @@ int32_t oracle_mig_select_candidate(const hs_mig_profile* profiles, uint32_t n, 
   if (profile_index) { *profile_index = -1; for (uint32_t i = 0; i < n; i++) if (ps[i].Name == pr.Name) { *profile_index = (int32_t)i; break; } }
   if (out) { out->start = pl.Start; out->size = pl.Size; }
   return 1;
+}
+float oracle_kunlun_calc_score(const int32_t* prev, uint32_t n_prev, const int32_t* cur, uint32_t n_cur) {
+  auto dedup = [](const int32_t* v, uint32_t n) {       // addidx, kunlun/topo.go:40-48
+    std::vector<int> out;
+    for (uint32_t i = 0; i < n; i++) if (std::find(out.begin(), out.end(), (int)v[i]) == out.end()) out.push_back((int)v[i]);
+    return out;
+  };
+  return KunlunCalcScore(dedup(prev, n_prev), dedup(cur, n_cur));
 }
 int32_t oracle_pod_delete(oracle_handle* o, const char* pod_uid) { return o->s->DeletePod(str(pod_uid)) ? HS_OK : HS_ERR_NOTFOUND; }
 

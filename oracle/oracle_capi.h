@@ -42,6 +42,8 @@ int32_t oracle_node_remove(oracle_handle* o, const char* name);
 int32_t oracle_usage_apply(oracle_handle* o, const char* pod_uid, const char* node, const char* uuid,
                            int32_t slots, int32_t usedmem, int32_t usedcores);
 int32_t oracle_pod_delete(oracle_handle* o, const char* pod_uid);
+/* calcscore (kunlun/topo.go:74-95) after addidx's dedup */
+float   oracle_kunlun_calc_score(const int32_t* prev, uint32_t n_prev, const int32_t* cur, uint32_t n_cur);
 /* dynamic MIG: the informer side and the state getNodesUsage derives (see hs_pod_set_mig / hs_snapshot_node_mig) */
 int32_t oracle_pod_set_mig(oracle_handle* o, const char* pod_uid, const hs_mig_reservation* res, uint32_t n);
 int32_t oracle_snapshot_node_mig(oracle_handle* o, const char* node, uint32_t* occupied, uint8_t* health, uint32_t cap);

@@ -129,6 +129,16 @@ def devs_array(devs):
     return arr
 
 
+def kunlun_calc_score(prev, cur):
+    """calcscore (kunlun/topo.go:74-95) on the card indices in use before / picked now"""
+    L = lib()
+    L.oracle_kunlun_calc_score.restype = C.c_float
+    L.oracle_kunlun_calc_score.argtypes = [C.POINTER(C.c_int32), C.c_uint32, C.POINTER(C.c_int32), C.c_uint32]
+    a = (C.c_int32 * max(1, len(prev)))(*prev)
+    b = (C.c_int32 * max(1, len(cur)))(*cur)
+    return L.oracle_kunlun_calc_score(a, len(prev), b, len(cur))
+
+
 def req_from_go(key, r):
     return {"key": key, "type": r.get("Type", ""), "nums": int(r.get("Nums", 0)), "memreq": int(r.get("Memreq", 0)),
             "mempct": int(r.get("MemPercentagereq", 0)), "coresreq": int(r.get("Coresreq", 0))}

@@ -366,8 +366,6 @@ def test_calc_score(orc, case):
     task = args.get("task") or {}
     annos = ((task.get("ObjectMeta") or {}).get("Annotations")) or {}
     n_init = len(((task.get("Spec") or {}).get("InitContainers")) or [])
-    if any(isinstance(r, dict) and "kunlun" in json.dumps(r) for r in args["nums"]):
-        pytest.skip("kunlun vendor is a 'next' row (SURVEY §8f N4)")
     pod = pod_from(annos, args["nums"], n_init, uid="task")
     want_nodes = {n["NodeID"]: n for n in ((case["wants"].get("want") or {}).get("NodeList") or [])}
     want_failed = case["wants"].get("failedNodes") if isinstance(case["wants"].get("failedNodes"), dict) else {}

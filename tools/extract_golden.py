@@ -335,7 +335,7 @@ IDENTS = {
     "AWSNeuronDevice": "AWSNeuron", "MetaxGPUDevice": "Metax-GPU", "MetaxGPUCommonWord": "Metax-GPU",
     "MthreadsGPUDevice": "Mthreads", "MthreadsUseUUID": "mthreads.ai/use-gpuuuid", "MthreadsNoUseUUID": "mthreads.ai/nouse-gpuuuid",
     "VastaiDevice": "Vastai", "VastaiUseUUID": "vastaitech.com/use-gpuuuid", "VastaiNoUseUUID": "vastaitech.com/nouse-gpuuuid",
-    "EnflameGCUDevice": "GCU",
+    "EnflameGCUDevice": "GCU", "KunlunGPUDevice": "kunlun", "KunlunGPUCommonWord": "kunlun", "kunlun.KunlunGPUDevice": "kunlun",
     "BirenDevice": "Biren", "BirenCommonWord": "Biren",
     "BirenUseUUID": "birentech.com/use-gpuuuid", "BirenNoUseUUID": "birentech.com/nouse-gpuuuid",
 }
@@ -464,6 +464,9 @@ TABLES = [
     ("metax_parse_annos", "pkg/device/metax/device_test.go", "TestParseMetaxAnnos", "tests"),
     ("metax_generate_requests", "pkg/device/metax/device_test.go", "Test_GenerateResourceRequests", "tests"),
     ("metax_get_node_devices", "pkg/device/metax/device_test.go", "TestGetNodeDevices", "tests"),
+    # kunlun whole XPUs: graghSelect over FitXPU, ScoreNode by wings
+    ("kunlun_graph_select", "pkg/device/kunlun/device_test.go", "Test_graphSelect", "tests"),
+    ("kunlun_score_node", "pkg/device/kunlun/device_test.go", "Test_ScoreNode", "tests"),
 ]
 
 
