@@ -285,7 +285,14 @@ enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
         * ScoreNode (:154-177): 0 unless every device of the node is a kunlun card, else 3000 / 2000 / 1000 / 0 by how
         * the "bubble" count of half-used wings changes (calcscore, topo.go:74-95).  Annotations: the allocated key and
         * BAIDU_COM_DEVICE_IDX = the card indices of the last container with devices (:93-110).  Card Index < 32.       */
-       HS_FIT_KUNLUN = 8 };
+       HS_FIT_KUNLUN = 8,
+       /* kunlun shared XPUs, type "XPU" (pkg/device/kunlun/vdevice.go:231-306): HS_FIT_KUNLUN's graghSelect with FitVXPU —
+        * healthy, Memreq + Usedmem <= Totalmem, and a card already in use only takes requests whose Memreq equals the
+        * card's average (Usedmem / Used); under the mutex policy only idle cards.  No slot count.  The pick records the
+        * request's Memreq / Coresreq, usage is added in full, ScoreNode is 0, both annotation keys are written.  Failure:
+        * under mutex the number of in-use cards that would otherwise fit ("ExclusiveDeviceAllocateConflict"), else the
+        * cards a uuid list turned away, else "1/n NumaNotFit".                                                          */
+       HS_FIT_KUNLUN_VXPU = 9 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */
@@ -425,6 +432,8 @@ enum { HS_REQ_NVIDIA = 0, HS_REQ_DCU = 1, HS_REQ_MLU = 2, HS_REQ_ASCEND = 3,
        HS_REQ_MTHREADS = 7,   /* mthreads/device.go:202-264: memory_factor 512; memory and cores divided by count */
        HS_REQ_WHOLE_CARD = 8, /* enflame/gcu.go:91-111: Memreq 100, MemPercentagereq 100, Coresreq 100            */
        HS_REQ_METAX = 9,      /* metax/device.go:134-154: Memreq 0, MemPercentagereq 100, Coresreq 100            */
+       HS_REQ_KUNLUN_VXPU = 11, /* kunlun/vdevice.go:173-213: count + memory trimmed up to 24576 / 49152 / 98304 MiB, cores =
+                               * the memory's share of a card in percent; no memory = the whole card                 */
        HS_REQ_NEURON = 10     /* awsneuron/device.go:287-334: by device (count_name) or by NeuronCore (cores_name, split
                                * over devices); default_cores = the vendor object's coresPerAWSNeuron                */
 };

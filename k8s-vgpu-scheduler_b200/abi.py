@@ -159,6 +159,7 @@ class hs_vendor_resources(C.Structure):
 
 HS_REQ_NVIDIA, HS_REQ_DCU, HS_REQ_MLU, HS_REQ_ASCEND = 0, 1, 2, 3
 HS_REQ_ILUVATAR, HS_REQ_COUNT, HS_REQ_AMD, HS_REQ_MTHREADS, HS_REQ_WHOLE_CARD, HS_REQ_METAX, HS_REQ_NEURON = 4, 5, 6, 7, 8, 9, 10
+HS_REQ_KUNLUN_VXPU = 11
 
 
 class hs_vendor_config(C.Structure):
@@ -168,7 +169,7 @@ class hs_vendor_config(C.Structure):
 
 
 HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD, HS_FIT_METAX, HS_FIT_NEURON, HS_FIT_VASTAI = 0, 1, 2, 3, 4, 5, 6, 7
-HS_FIT_KUNLUN = 8
+HS_FIT_KUNLUN, HS_FIT_KUNLUN_VXPU = 8, 9
 
 # The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
 # (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
@@ -195,6 +196,9 @@ DEFAULT_VENDORS = [
      "hami.io/aws-neuron-devices-allocated"),
     # kunlun whole XPUs (kunlun/device.go:32-56): SupportDevices only; the second uuid pair (baidu.com/...) is fixed in the Fit
     ("kunlun", HS_FIT_KUNLUN, "hami.io/use-xpu-uuid", "hami.io/no-use-xpu-uuid", None, "hami.io/kunlun-allocated"),
+    # kunlun shared XPUs (kunlun/vdevice.go:34-63)
+    ("XPU", HS_FIT_KUNLUN_VXPU, "hami.io/use-xpu-uuid", "hami.io/no-use-xpu-uuid", "hami.io/xpu-devices-to-allocate",
+     "hami.io/xpu-devices-allocated"),
 ]
 
 

@@ -164,6 +164,7 @@ struct VendorInfo {
   int fit_kind = 0;         // HS_FIT_* as registered (hs_filter_simulate hands it on to the child handle)
   bool vastai = false;      // vastai: count-only gates + die mode (EF_VASTAI)
   bool kunlun = false;      // kunlun whole XPUs: graghSelect, slot-only usage, wing ScoreNode (EF_KUNLUN)
+  bool vxpu = false;        // … the shared "XPU" type on the same graghSelect (EF_KUNLUN | EF_VXPU)
   bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
   std::vector<std::pair<std::string, int64_t>> templates;  // sorted by memory
 };
@@ -711,6 +712,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       if (v && v->neuron) e.flags |= EF_NEURON;
       if (v && v->whole_card) e.flags |= EF_WHOLE_CARD;
       if (v && v->kunlun) e.flags |= EF_KUNLUN;
+      if (v && v->vxpu) e.flags |= EF_VXPU;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
       if (v && v->ascend910) e.flags |= EF_ASCEND910;
@@ -1476,7 +1478,7 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
         }
         continue;
       }
-      if (v.kunlun) {     // kunlun/device.go:93-110: the allocated key; the card indices of the LAST container with devices
+      if (v.kunlun && !v.vxpu) {     // kunlun/device.go:93-110: the allocated key; the card indices of the LAST container with devices
         annos[v.allocated] = s;
         for (auto& ctr : it->second) {
           std::string value;
@@ -2223,7 +2225,8 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.whole_card = vc.fit_kind == HS_FIT_WHOLE_CARD;
       v.metax = vc.fit_kind == HS_FIT_METAX;
       v.neuron = vc.fit_kind == HS_FIT_NEURON;
-      v.kunlun = vc.fit_kind == HS_FIT_KUNLUN;
+      v.kunlun = vc.fit_kind == HS_FIT_KUNLUN || vc.fit_kind == HS_FIT_KUNLUN_VXPU;
+      v.vxpu = vc.fit_kind == HS_FIT_KUNLUN_VXPU;
       if (v.metax) { v.use_uuid.clear(); v.nouse_uuid.clear(); }   // checkUUID is constant true (metax/device.go:124-126)
       if (vc.use_type_key) v.use_type = vc.use_type_key;
       if (vc.nouse_type_key) v.nouse_type = vc.nouse_type_key;

@@ -254,13 +254,19 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
     if (e.nouse_cnt) nouseMaskK = uuid_mask_lookup(ka.uuid_pool, e.nouse_off, e.nouse_cnt, node);
     uint32_t fit = 0;              // by list position
     int idx[HS_D];
-    int mism = 0, left = 0, right = 0;
+    int mism = 0, left = 0, right = 0, excl = 0;
+    const bool vxpu = e.flags & EF_VXPU;
     for (int i = 0; i < cnt; i++) {
       const int d = td[i];
       idx[i] = (int)PK_INDEX(w.packed[d]);
       const bool uu = ((useMaskK >> d) & 1u) && !((nouseMaskK >> d) & 1u);
+      // FitVXPU, vdevice.go:293-306 (int32 arithmetic as in Go)
+      const bool vfit = (w.dflags[d] & DF_HEALTH) && !((int)((unsigned)e.memreq + (unsigned)w.mem[d]) > w.totmem[d]) &&
+                        (w.used[d] == 0 || w.mem[d] / w.used[d] == e.memreq);
+      if (vxpu && isMutex && w.used[d] > 0 && vfit) excl++;        // vdevice.go:259-266 counts these whatever the uuid lists say
       if (!uu) { mism++; continue; }
-      if (w.used[d] == 0 && (w.dflags[d] & DF_HEALTH)) { fit |= 1u << i; if (i < 4) left++; else right++; }
+      const bool ok = vxpu ? ((!isMutex || w.used[d] == 0) && vfit) : (w.used[d] == 0 && (w.dflags[d] & DF_HEALTH));
+      if (ok) { fit |= 1u << i; if (i < 4) left++; else right++; }
     }
     const int count = e.nums;
     int alloc[HS_D], na = 0;
@@ -310,7 +316,11 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
       }
     }
     if (na == 0) {
-      if (MODE == EV_EXPLAIN) { if (mism > 0) out.reasons[1] += (uint32_t)mism; else out.reasons[8]++; }
+      if (MODE == EV_EXPLAIN) {
+        if (excl > 0) out.reasons[9] += (uint32_t)excl;
+        else if (mism > 0) out.reasons[1] += (uint32_t)mism;
+        else out.reasons[8]++;
+      }
       return false;
     }
     for (int a = 0; a < na; a++)
@@ -318,8 +328,8 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
         const int d = td[i];
         if ((int)PK_INDEX(w.packed[d]) != alloc[a]) continue;
         fc.tmp_dev[fc.ntmp] = d;
-        fc.tmp_mem[fc.ntmp] = w.totmem[d];
-        fc.tmp_cores[fc.ntmp] = w.totcore[d];
+        fc.tmp_mem[fc.ntmp] = vxpu ? e.memreq : w.totmem[d];
+        fc.tmp_cores[fc.ntmp] = vxpu ? e.coresreq : w.totcore[d];
         fc.ntmp++;
         break;
       }
@@ -691,7 +701,12 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
         if (w.aws[d] < 0) w.aws[d] = 0;
         w.aws[d] += fc.tmp_aws[t];
       }
-      if (e.flags & EF_KUNLUN) {          // kunlun/device.go:179-182: AddResourceUsage counts the slot only; the pick keeps the whole card
+      if (e.flags & EF_VXPU) {
+        pick_cores = fc.tmp_cores[t];     // the request's Coresreq as asked (vdevice.go:283)
+        w.used[d] += 1;
+        w.cores[d] += pick_cores;
+        w.mem[d] += fc.tmp_mem[t];
+      } else if (e.flags & EF_KUNLUN) {   // kunlun/device.go:179-182: AddResourceUsage counts the slot only; the pick keeps the whole card
         pick_cores = fc.tmp_cores[t];
         w.used[d] += 1;
         const int ki = (int)PK_INDEX(w.packed[d]);
@@ -749,7 +764,7 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   w.kl_cur = 0;
   uint32_t kl_prev = 0;               // kunlun ScoreNode's `previous`: cards in use before the pod (score.SnapshotDevice, score.go:328)
   bool has_kunlun = false;
-  for (int e = 0; e < pod.n_entries; e++) if (ent[e].flags & EF_KUNLUN) has_kunlun = true;
+  for (int e = 0; e < pod.n_entries; e++) if ((ent[e].flags & EF_KUNLUN) && !(ent[e].flags & EF_VXPU)) has_kunlun = true;
   if (has_kunlun)
     for (int d = 0; d < w.ndev; d++) if (w.used[d] > 0 && PK_INDEX(w.packed[d]) < 32) kl_prev |= 1u << PK_INDEX(w.packed[d]);
   uint32_t metax_slots = 0;           // score slots that belong to a metax type (their accumulator is a device count)

@@ -180,6 +180,13 @@ bool generate(const hs_vendor_resources& v, const hs_container_resources* c, hs_
       corenum = corenum / (int32_t)n;
       break;
     }
+    case HS_REQ_KUNLUN_VXPU: {                                // kunlun/vdevice.go:173-213: memory rounded up to 24576 / 49152 / 98304
+      if (mem && mem->as_int64_ok) memnum = mem->as_int64 <= 24576 ? 24576 : (mem->as_int64 <= 49152 ? 49152 : 98304);   // trimMemory, :62-70
+      corenum = (int32_t)(memnum * 100 / 98304);
+      mempnum = 0;
+      if (memnum == 0) { mempnum = 100; corenum = 100; memnum = 98304; }
+      break;
+    }
     default:
       return false;
   }

@@ -69,6 +69,7 @@ enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
 #define EF_AMD 16u         // amd's Fit (amd/device.go:279-371): whole-card memory by default, cores as a share of the card
 #define EF_VASTAI 512u     // vastai: EF_COUNT_ONLY gates; on a node of dies (NetworkID = AIC) card exclusivity under mutex, pick by card, ScoreNode
 #define EF_KUNLUN 1024u    // kunlun whole XPUs (kunlun/device.go:184-240, topo.go): graghSelect over list positions, slot-only usage, ScoreNode by wings
+#define EF_VXPU 2048u      // with EF_KUNLUN: the shared "XPU" type (kunlun/vdevice.go:231-306): FitVXPU, full usage, no ScoreNode
 #define EF_COUNT_ONLY 8u   // biren's Fit (biren/device.go:190-248): gates end after mutex; the pick has Usedmem 0, Usedcores = Coresreq
 
 struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 64 B

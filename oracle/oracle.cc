@@ -1135,7 +1135,18 @@ FitResult fitNeuron(const FitGates& g, const std::vector<DeviceUsage*>& devices,
 // Fit runs graghSelect over the typeDevices in LIST order (wings = positions 0-3 / 4-7), FitXPU = idle and healthy,
 // the two use/no-use uuid annotation pairs applied inside fitFn; a failure reads the number of devices a uuid list
 // turned away, else one NumaNotFit.
-FitResult fitKunlun(const std::string& word, const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod) {
+// vxpu = the shared "XPU" device type (kunlun/vdevice.go:231-306): the same graghSelect with FitVXPU — healthy, the
+// request's memory still fits, and a card in use only takes requests of the size it already serves (its average) —
+// idle cards only under the mutex policy; the pick records the request's memory and cores.
+static bool fitVXPU(const DeviceUsage& d, const ContainerDeviceRequest& request) {          // vdevice.go:293-306
+  if (!d.Health) return false;
+  if (i32add(request.Memreq, d.Usedmem) > d.Totalmem) return false;
+  if (d.Used == 0) return true;
+  return d.Usedmem / d.Used == request.Memreq;
+}
+FitResult fitKunlun(const std::string& word, const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
+                    bool vxpu, const std::string& gpuPolicyDefault) {
+  const bool isMutex = vxpu && PolicyContains(GetGPUSchedulerPolicyByPod(gpuPolicyDefault, pod), "mutex");
   std::set<std::string> uuidMismatches;
   std::vector<bool> fit;
   std::vector<int> index;
@@ -1145,7 +1156,8 @@ FitResult fitKunlun(const std::string& word, const std::vector<DeviceUsage*>& de
         !CheckUUID(pod.Annotations, d->ID, "baidu.com/use-gpuuuid", "baidu.com/nouse-gpuuuid")) {
       uuidMismatches.insert(d->ID);
       ok = false;
-    } else ok = d->Used == 0 && d->Health;            // FitXPU, :238-240
+    } else if (vxpu) ok = (!isMutex || d->Used == 0) && fitVXPU(*d, request);
+    else ok = d->Used == 0 && d->Health;            // FitXPU, device.go:238-240
     fit.push_back(ok);
     index.push_back((int)d->Index);
   }
@@ -1153,8 +1165,10 @@ FitResult fitKunlun(const std::string& word, const std::vector<DeviceUsage*>& de
   FitResult r;
   if (alloc.empty()) {
     std::map<std::string, int> reason;
-    if (!uuidMismatches.empty()) reason["CardUuidMismatch"] += (int)uuidMismatches.size();
-    else reason["NumaNotFit"]++;
+    if (isMutex)                                     // vdevice.go:259-266
+      for (auto d : devices) if (d->Used > 0 && fitVXPU(*d, request)) reason["ExclusiveDeviceAllocateConflict"]++;
+    if (reason.empty() && !uuidMismatches.empty()) reason["CardUuidMismatch"] += (int)uuidMismatches.size();
+    if (reason.empty()) reason["NumaNotFit"]++;
     r.fit = false; r.reason = GenReason(reason, (int)devices.size());
     return r;
   }
@@ -1162,7 +1176,9 @@ FitResult fitKunlun(const std::string& word, const std::vector<DeviceUsage*>& de
     for (auto val : devices)
       if (val->Index == (unsigned)dev) {
         ContainerDevice cd;
-        cd.Idx = (int)val->Index; cd.UUID = val->ID; cd.Type = request.Type; cd.Usedmem = val->Totalmem; cd.Usedcores = val->Totalcore;
+        cd.Idx = (int)val->Index; cd.UUID = val->ID; cd.Type = request.Type;
+        cd.Usedmem = vxpu ? request.Memreq : val->Totalmem;
+        cd.Usedcores = vxpu ? request.Coresreq : val->Totalcore;
         r.devs.push_back(cd);
         break;
       }
@@ -1181,7 +1197,7 @@ class PlainDevices : public Devices {
                 const QuotaManager* quota) const override {
     static const Vendor kinds[] = {Vendor::PLAIN, Vendor::COUNT_ONLY, Vendor::AMD, Vendor::MTHREADS, Vendor::WHOLE_CARD, Vendor::METAX,
                                    Vendor::PLAIN /* 6 = Neuron, below */, Vendor::VASTAI};
-    if (v_.FitKind == 8) return fitKunlun(v_.CommonWord, devices, request, pod);
+    if (v_.FitKind == 8 || v_.FitKind == 9) return fitKunlun(v_.CommonWord, devices, request, pod, v_.FitKind == 9, def);
     FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 7 ? v_.FitKind : 0],
                v_.CommonWord,
                v_.UseType, v_.NoUseType, v_.UseUUID, v_.NoUseUUID};

@@ -95,6 +95,52 @@ def test_fit_reasons_and_uuid_annotations(orc):
     assert ok and [g[0] for g in got] == ["xpu-2"]
 
 
+# ---- the shared "XPU" type (kunlun/vdevice.go) ------------------------------------------------------------------------
+def fit_vxpu(orc, devices, request, annos=None):
+    ok, got, reason = run_fit(orc, "XPU", devices, dict(request, Type="XPU"), annos or {})
+    return ok, [g[1] for g in got], got, reason
+
+
+@pytest.mark.parametrize("case", load("kunlun_graph_select_vxpu"), ids=ids(load("kunlun_graph_select_vxpu")))
+def test_graph_select_vxpu_table(orc, case):
+    # kunlun/device_test.go:281-417: graghSelect with FitVXPU
+    devs = [dict(d, ID="xpu-%d" % d["Index"], Type="XPU", Totalcore=100) for d in case["args"]["d"]]
+    ok, idx, got, _ = fit_vxpu(orc, devs, case["args"]["c"])
+    assert idx == list(case["want1"] or []) and ok == bool(case["want1"])
+    for g in got:
+        assert g[2] == case["args"]["c"].get("Memreq", 0)       # the pick records the request's memory (vdevice.go:282)
+
+
+@pytest.mark.parametrize("case", load("kunlun_fit_vxpu_direct"), ids=ids(load("kunlun_fit_vxpu_direct")))
+def test_fit_vxpu_direct(orc, case):
+    # kunlun/vdevice_test.go:498-541: one card, one device asked
+    dev = dict(case["usage"], ID="xpu-0", Index=0, Type="XPU")
+    ok, _, _, _ = fit_vxpu(orc, [dev], dict(case["request"], Nums=1))
+    assert ok == case["want"]
+
+
+def test_vxpu_fit_reasons(orc):
+    # device_test.go:32-55 (TestKunlunVDevices_Fit_Mutex): shareable cards, all in use
+    devs = [{"ID": "x%d" % i, "Index": i, "Used": 1, "Usedmem": 24576, "Totalmem": 98304, "Health": True, "Type": "XPU"} for i in range(8)]
+    assert fit_vxpu(orc, devs, {"Nums": 1, "Memreq": 24576})[0] is True
+    ok, _, _, reason = fit_vxpu(orc, devs, {"Nums": 1, "Memreq": 24576}, {"hami.io/gpu-scheduler-policy": "mutex"})
+    assert not ok and reason == "8/8 ExclusiveDeviceAllocateConflict"
+    # device_test.go:57-68 (TestKunlunVDevices_Fit_NumaNotFit)
+    devs = [{"ID": "x%d" % i, "Index": i, "Used": 0, "Usedmem": 0, "Totalmem": 1024, "Type": "XPU"} for i in range(8)]
+    ok, _, _, reason = fit_vxpu(orc, devs, {"Nums": 1, "Memreq": 2048})
+    assert not ok and reason == "1/8 NumaNotFit"
+    # device_test.go:609-651 (TestKunlunVDevices_Fit_UUIDAnnotations)
+    devs = [{"ID": "xpu-%d" % i, "Index": i, "Count": 10, "Totalmem": 98304, "Totalcore": 100, "Health": True, "Type": "XPU"} for i in range(8)]
+    req = {"Nums": 1, "Memreq": 98304}
+    for key, want in (("hami.io/use-xpu-uuid", "xpu-3"), ("baidu.com/use-gpuuuid", "xpu-2")):
+        ok, _, got, _ = fit_vxpu(orc, devs, req, {key: want})
+        assert ok and got[0][0] == want
+    every = ",".join("xpu-%d" % i for i in range(8))
+    for key in ("hami.io/no-use-xpu-uuid", "baidu.com/nouse-gpuuuid"):
+        ok, _, _, reason = fit_vxpu(orc, devs, req, {key: every})
+        assert not ok and "CardUuidMismatch" in reason
+
+
 # ---- GPU parity ----------------------------------------------------------------------------------------------------
 def _kunlun_node(name, cards=8, extra=None):
     devs = [{"id": "%s-kunlun-%d" % (name, i), "index": i, "count": 100, "devmem": 98304, "devcore": 100, "type": "kunlun",
@@ -102,7 +148,7 @@ def _kunlun_node(name, cards=8, extra=None):
     return {"name": name, "devices": devs + (extra or [])}
 
 
-def _kunlun_cluster(seed, n_nodes=40, n_pods=700):
+def _kunlun_cluster(seed, n_nodes=40, n_pods=900):
     import random
     rng = random.Random(seed)
     nodes = []
@@ -125,6 +171,11 @@ def _kunlun_cluster(seed, n_nodes=40, n_pods=700):
                 {"id": "%s-gpu-%d" % (name, j), "index": j, "count": 10, "devmem": 81920, "devcore": 100, "type": "NVIDIA-H100",
                  "numa": j // 4, "mode": "hami-core", "health": True, "vendor": "NVIDIA"} for j in range(8)]}
         nodes.append(n)
+    for i in range(n_nodes // 3):                            # shared XPUs (registered from hami.io/node-register-xpu in the reference)
+        name = "vx-%02d" % i
+        nodes.append({"name": name, "devices": [
+            {"id": "%s-xpu-%d" % (name, j), "index": j, "count": 10, "devmem": 98304, "devcore": 100, "type": "XPU-P800",
+             "numa": j // 4, "mode": "", "health": rng.random() > 0.05, "vendor": "XPU"} for j in range(8)]})
     kl_nodes = [n for n in nodes if any(d["vendor"] == "kunlun" for d in n["devices"])]
     ops, live = [], []
     for p in range(n_pods):
@@ -149,10 +200,21 @@ def _kunlun_cluster(seed, n_nodes=40, n_pods=700):
                 annos[key2] = ",".join(rng.sample(ids_, rng.randint(1, len(ids_))))
         kl = lambda n: {"key": "kunlun", "type": "kunlun", "nums": n, "memreq": 0, "mempct": 100, "coresreq": 0}  # noqa: E731
         nv = lambda n: {"key": "NVIDIA", "type": "NVIDIA", "nums": n, "memreq": 8000, "mempct": 101, "coresreq": 10}  # noqa: E731
+        vx = lambda n, m: {"key": "XPU", "type": "XPU", "nums": n, "memreq": m, "mempct": 0 if m != 98304 else 100,  # noqa: E731
+                           "coresreq": m * 100 // 98304}
         r = rng.random()
-        if r < 0.12:
+        if r < 0.3:
+            ctrs = [[vx(rng.choice([1, 1, 2, 4, 8, 3]), rng.choice([24576, 24576, 49152, 98304]))]]
+            if rng.random() < 0.2:
+                ctrs.append([vx(rng.choice([1, 2]), rng.choice([24576, 49152]))])
+            if rng.random() < 0.2:
+                annos["hami.io/gpu-scheduler-policy"] = "mutex"
+            if rng.random() < 0.1:
+                annos[rng.choice(["hami.io/use-xpu-uuid", "baidu.com/nouse-gpuuuid"])] = ",".join(
+                    "vx-%02d-xpu-%d" % (rng.randrange(n_nodes // 3), rng.randrange(8)) for _ in range(rng.randint(1, 5)))
+        elif r < 0.38:
             ctrs = [[nv(rng.choice([1, 2]))]]
-        elif r < 0.2:
+        elif r < 0.45:
             ctrs = [[kl(rng.choice([1, 2])), nv(1)]]          # both vendors in one container: only the mixed nodes can serve it
         else:
             ctrs = [[kl(rng.choice([1, 1, 2, 2, 4, 4, 8, 3]))]]
@@ -177,12 +239,15 @@ def test_kunlun_gpu_parity(seed):
     assert parity.compare(ops, ref, got, ref_snap, snap) == []
     fits = [r for (k, a), r in zip(ops, ref) if k == "filter" and r["status"] == abi.HS_FIT and any(r["devices"].get("kunlun", []))]
     nofit = [r for (k, a), r in zip(ops, ref) if k == "filter" and r["status"] == abi.HS_NOFIT]
-    assert len(fits) > 150 and len(nofit) > 20
+    assert len(fits) > 100 and len(nofit) > 20
     scores = {round(r["score"]) // 1000 for r in fits}
     assert len(scores) >= 3                                  # the wing score moved the node choice around (0 / 1000 / 2000 / 3000 + usage)
     assert any("CardUuidMismatch" in v for r in nofit for v in r["failed"].values())
     assert any("NumaNotFit" in v for r in nofit for v in r["failed"].values())
     assert all("hami.io/kunlun-allocated" in r["annotations"] and "BAIDU_COM_DEVICE_IDX" in r["annotations"] for r in fits)
+    vfits = [r for (k, a), r in zip(ops, ref) if k == "filter" and r["status"] == abi.HS_FIT and any(r["devices"].get("XPU", []))]
+    assert len(vfits) > 60 and all("hami.io/xpu-devices-allocated" in r["annotations"] and "hami.io/xpu-devices-to-allocate" in r["annotations"] for r in vfits)
+    assert any("ExclusiveDeviceAllocateConflict" in v for r in nofit for v in r["failed"].values())
     # the same all-kunlun nodes registered from capacity (kunlun/device.go:64-91) decide identically
     e = eng.Engine(cfg.get("node_policy"), cfg.get("gpu_policy"))
     n_cap = 0

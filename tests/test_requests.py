@@ -143,6 +143,13 @@ def oracle_generate(v, limits, requests):
         pctn = 100 if memnum == 0 else 0
     elif v["kind"] == abi.HS_REQ_COUNT:          # biren/device.go:141-165, vastai/device.go:143-167
         memnum, pctn, cores = 0, 100, 0
+    elif v["kind"] == abi.HS_REQ_KUNLUN_VXPU:    # kunlun/vdevice.go:173-213 (trimMemory :62-70)
+        if mem is not None and mem[1]:
+            memnum = 24576 if mem[0] <= 24576 else (49152 if mem[0] <= 49152 else 98304)
+        cores = memnum * 100 // 98304
+        pctn = 0
+        if memnum == 0:
+            memnum, pctn, cores = 98304, 100, 100
     elif v["kind"] == abi.HS_REQ_WHOLE_CARD:     # enflame/gcu.go:91-111
         memnum, pctn, cores = 100, 100, 100
     elif v["kind"] == abi.HS_REQ_METAX:          # metax/device.go:134-154
@@ -245,6 +252,8 @@ MTHREADS = _plain("Mthreads", abi.HS_REQ_MTHREADS, "mthreads.com/vgpu", "mthread
 GCU = _plain("GCU", abi.HS_REQ_WHOLE_CARD, "enflame.com/gcu")
 AMD = _plain("AMD", abi.HS_REQ_AMD, "amd.com/gpu", "amd.com/gpu-mem", "amd.com/gpu-core-pct")
 METAX = _plain("Metax-GPU", abi.HS_REQ_METAX, "metax-tech.com/gpu")
+# the golden table keeps the Go identifiers of the two resource names as its map keys (vdevice_test.go:430,444-445)
+XPU = _plain("XPU", abi.HS_REQ_KUNLUN_VXPU, "KunlunResourceVCount", "KunlunResourceVMemory")
 NEURON = dict(_plain("AWSNeuron", abi.HS_REQ_NEURON, "aws.amazon.com/neuron", None, "aws.amazon.com/neuroncore"), default_cores=2)
 
 TABLES = [("nvidia_generate_requests", NVIDIA, 15), ("hygon_generate_requests", DCU, 5), ("hygon_generate_requests_range", DCU, 2),
@@ -252,7 +261,7 @@ TABLES = [("nvidia_generate_requests", NVIDIA, 15), ("hygon_generate_requests", 
           ("ascend_generate_requests_range", ASCEND_CORE, 7),
           ("iluvatar_generate_requests", ILUVATAR, 5), ("biren_generate_requests", BIREN, 4), ("vastai_generate_requests", VASTAI, 4),
           ("mthreads_generate_requests", MTHREADS, 8), ("gcu_generate_requests", GCU, 3), ("metax_generate_requests", METAX, 2),
-          ("awsneuron_generate_requests", NEURON, 8)]
+          ("awsneuron_generate_requests", NEURON, 8), ("kunlun_vxpu_generate_requests", XPU, 3)]
 
 
 @pytest.mark.parametrize("name,vendor,count", TABLES, ids=[t[0] for t in TABLES])
@@ -313,7 +322,7 @@ def test_product_matches_restatement_on_random_containers():
     rng = random.Random(42)
     vendors = [NVIDIA, dict(NVIDIA, word="NV2", factor=4, default_mem=777, default_cores=5), DCU, dict(DCU, word="DCU2", factor=3),
                MLU, ASCEND_910A, ASCEND_CORE, dict(ASCEND_CORE, word="AscF", factor=2),
-               ILUVATAR, BIREN, MTHREADS, GCU, AMD, METAX, NEURON, dict(NEURON, word="Neuron1", default_cores=1),
+               ILUVATAR, BIREN, MTHREADS, GCU, AMD, METAX, XPU, NEURON, dict(NEURON, word="Neuron1", default_cores=1),
                dict(NEURON, word="Neuron0", default_cores=0)]
     names = sorted({v[k] for v in vendors for k in ("count", "mem", "pct", "cores") if v[k]})
     pool = [0, 1, 2, 8, -1, -100, 100, 101, 150, 4096, 2 ** 31 - 1, 2 ** 31, 2200000000, 2 ** 32 + 50, 8388607, 8388608,

@@ -336,6 +336,8 @@ IDENTS = {
     "MthreadsGPUDevice": "Mthreads", "MthreadsUseUUID": "mthreads.ai/use-gpuuuid", "MthreadsNoUseUUID": "mthreads.ai/nouse-gpuuuid",
     "VastaiDevice": "Vastai", "VastaiUseUUID": "vastaitech.com/use-gpuuuid", "VastaiNoUseUUID": "vastaitech.com/nouse-gpuuuid",
     "EnflameGCUDevice": "GCU", "KunlunGPUDevice": "kunlun", "KunlunGPUCommonWord": "kunlun", "kunlun.KunlunGPUDevice": "kunlun",
+    "XPUDevice": "XPU", "KunlunResourceVCount": "kunlunxin.com/vxpu", "KunlunResourceVMemory": "kunlunxin.com/vxpu-memory",
+    "KunlunMaxMemory": 98304,
     "BirenDevice": "Biren", "BirenCommonWord": "Biren",
     "BirenUseUUID": "birentech.com/use-gpuuuid", "BirenNoUseUUID": "birentech.com/nouse-gpuuuid",
 }
@@ -467,6 +469,10 @@ TABLES = [
     # kunlun whole XPUs: graghSelect over FitXPU, ScoreNode by wings
     ("kunlun_graph_select", "pkg/device/kunlun/device_test.go", "Test_graphSelect", "tests"),
     ("kunlun_score_node", "pkg/device/kunlun/device_test.go", "Test_ScoreNode", "tests"),
+    # kunlun shared XPUs ("XPU"): the same graghSelect with FitVXPU, and the request extraction with trimMemory
+    ("kunlun_graph_select_vxpu", "pkg/device/kunlun/device_test.go", "Test_graphSelectVXPU", "tests"),
+    ("kunlun_vxpu_generate_requests", "pkg/device/kunlun/vdevice_test.go", "Test_KunlunVDevices_GenerateResourceRequests", "tests"),
+    ("kunlun_fit_vxpu_direct", "pkg/device/kunlun/vdevice_test.go", "Test_FitVXPU_direct", "tests"),
 ]
 
 
