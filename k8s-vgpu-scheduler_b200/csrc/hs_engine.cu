@@ -235,6 +235,7 @@ struct hs_handle {
   uint64_t launches = 0;
   int block = 256;          // threads per CTA of the decide kernel: 8 lanes per node
   bool no_fast = false;     // HS_NO_FAST=1: force the general evaluator (A/B testing of the two device paths)
+  bool no_resident = false; // HS_NO_RESIDENT=1: force the streaming mode of the decide loop (tests: the lane-dealt general path on small inventories)
 
   std::vector<VendorInfo> vendors;
   std::unordered_map<std::string, int> vendor_by_word;
@@ -1047,6 +1048,7 @@ int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_ca
   memset(&ka, 0, sizeof ka);
   ka.dyn = h->d_dyn; ka.stat = h->d_stat; ka.node_flags = h->d_flags; ka.node_tot = h->d_tot; ka.pair = h->d_pair;
   ka.mig_tab = h->has_mig ? h->d_mig_tab : nullptr;
+  ka.no_resident = h->no_resident ? 1 : 0;
   ka.n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
   ka.cand_pos = h->have_cand ? h->b_candpos.d : nullptr;
   ka.pods = h->b_pods.d; ka.entries = h->b_entries.d; ka.uuid_pool = h->b_uuid.d; ka.rel_pool = h->b_rel.d;
@@ -2239,6 +2241,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   const char* blk = getenv("HS_BLOCK");
   if (blk) { int b = atoi(blk); if (b >= 32 && b <= 512 && b % 32 == 0) h->block = b; }
   h->no_fast = getenv("HS_NO_FAST") != nullptr;
+  h->no_resident = getenv("HS_NO_RESIDENT") != nullptr;
   h->force_shard = getenv("HS_FORCE_SHARD") != nullptr;
   h->shard_use_nccl = getenv("HS_SHARD_NCCL") != nullptr;
   h->hostprof = getenv("HS_HOSTPROF") != nullptr;

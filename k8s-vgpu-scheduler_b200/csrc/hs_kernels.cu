@@ -366,7 +366,7 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
   const uint32_t gmask = 0xffu << gbase;
   const int gg = gtid >> 3;                   // node-owner group id
   const int ngroups = (gridDim.x * blockDim.x) >> 3;
-  const bool resident = ka.n_nodes <= ngroups;  // every group owns at most one node: it stays in registers
+  const bool resident = ka.n_nodes <= ngroups && !ka.no_resident;  // every group owns at most one node: it stays in registers
 
   DevRegs D;                   // the owned device (resident mode), kept current by this group's own commits
   D.used = D.mem = D.cores = D.count = D.totmem = D.totcore = 0;
@@ -527,6 +527,7 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
 
     // ---- sweep: every group evaluates the node(s) it owns --------------------------------------
     unsigned long long my_key = 0;   // same value in all 8 lanes of a group
+    unsigned long long t_key = 0;    // general path: the best key among the nodes THIS thread evaluated
     int my_node = -1;
     float my_score = 0.0f;
     uint32_t my_nalloc = 0;
@@ -584,12 +585,16 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
         }
       }
     } else if constexpr (GENERAL) {
-      // general evaluator: one thread (lane 0 of the group) per node
-      if (glane == 0) {
+      // general evaluator: one thread per node.  Resident mode: lane 0 of the group that holds the node.  Streaming
+      // mode: the group's node list {gg, gg + ngroups, …} is dealt to its 8 lanes, so a node is always evaluated — and,
+      // when it wins, committed — by the same thread, and the 20 000-node configs use every lane instead of one in 8.
+      t_key = 0ull;
+      if (glane == 0 || !resident) {
         NodeWork w;
         EvalOut out;
         DevAlloc tmp[HS_MAX_ALLOC];
-        for (int node = gg; node < ka.n_nodes; node += ngroups) {
+        const int first = resident ? gg : gg + glane * ngroups, stride = resident ? ngroups : ngroups * HS_D;
+        for (int node = first; node < ka.n_nodes; node += stride) {
           const uint32_t nf = ka.node_flags[node];
           if (!(nf & NF_ALIVE)) continue;
           const int pos = ka.cand_pos ? ka.cand_pos[node] : node;
@@ -599,15 +604,20 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
           float sc;
           if (dev_score_node<EV_RECORD>(w, pod, ent, (uint32_t)node, nf, ka, out, &sc)) {
             const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
-            if (key > my_key) {
-              my_key = key; my_node = node; my_score = sc; my_nalloc = out.n_alloc;
+            if (key > t_key) {
+              t_key = key; my_node = node; my_score = sc; my_nalloc = out.n_alloc;
               for (uint32_t i = 0; i < out.n_alloc; i++) la[i] = tmp[i];
             }
           }
         }
       }
-      my_key = __shfl_sync(FULL, my_key, gbase);
-      my_node = __shfl_sync(FULL, my_node, gbase);
+      // the group's key = the best of its lanes (my_key stays uniform within the group; my_node etc. stay the thread's own)
+      my_key = t_key;
+#pragma unroll
+      for (int o = 1; o < HS_D; o <<= 1) {
+        const unsigned long long t = __shfl_xor_sync(FULL, my_key, o);
+        my_key = t > my_key ? t : my_key;
+      }
     }
     TICK(2);
 
@@ -712,7 +722,7 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
         }
       } else if (GENERAL && mine) {
         if constexpr (GENERAL) {
-        if (glane == 0) {
+        if (t_key == win) {          // the one thread that evaluated the winning node
           int4 delta[HS_D];
           collapse_rows(ent, la, my_nalloc, delta);
           const uint32_t off = pod.alloc_base;
@@ -757,12 +767,13 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
             if (glane == 0) fb[node] = pos >= 0 ? f : nc;
           }
         }
-      } else if (GENERAL && glane == 0) {
+      } else if (GENERAL && (glane == 0 || !resident)) {
         if constexpr (GENERAL) {
         DevFail* fb = ka.fail + (size_t)fail_count * ka.n_nodes;
         NodeWork w;
         EvalOut out;
-        for (int node = gg; node < ka.n_nodes; node += ngroups) {
+        const int first = resident ? gg : gg + glane * ngroups, stride = resident ? ngroups : ngroups * HS_D;
+        for (int node = first; node < ka.n_nodes; node += stride) {
           const uint32_t nf = ka.node_flags[node];
           DevFail f;
           f.kind_cards = FK_NOT_CANDIDATE; f.c0 = f.c1 = f.pad = 0;

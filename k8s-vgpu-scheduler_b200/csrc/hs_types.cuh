@@ -220,6 +220,7 @@ struct KernelArgs {
   const uint32_t* node_flags;
   int4* node_tot;               // per node {flags, float bits of ComputeDefaultScore on the current usage, 0, 0}: kept current by every commit/release
   const int16_t* pair;          // [node][64]
+  int32_t no_resident;          // test knob (HS_NO_RESIDENT=1): take the streaming mode even when the inventory would stay in registers
   const MigGeom* mig_tab;       // MIG geometries by PK_GEOM (entry 0 is empty); NULL while no GPU in MIG mode is registered
   int32_t n_nodes;              // slots (padded to HS_TILE)
   // candidate positions: NULL = every alive node, position == slot

@@ -7,6 +7,7 @@ import os
 import pytest
 
 import parity
+import oracle_abi as oa
 from oracle_abi import abi
 
 pytestmark = pytest.mark.gpu
@@ -134,7 +135,15 @@ def test_golden_filter_cases_on_gpu():
         assert [out["node"]] == case["want"]["NodeNames"], case["name"]
         anno = out["annotations"]["hami.io/vgpu-devices-allocated"]
         ids = [seg.split(",")[0] for ctr in anno.split(";") for seg in ctr.split(":") if "," in seg]
-        assert ids and ids[-1] in case["wantPodAnnotationDeviceIDs"], case["name"]
+        assert ids and ids[-1] in case["wantPodAnnotationDeviceIDs"], case["name"]     # what the reference's test accepts …
+        o = oa.Oracle()                                                                   # … and the ONE answer the canonical rule pins
+        for n in M["nodes"]:
+            o.node_upsert(n)
+        for uid, node, uuid, mem, cores in M["pods"]:
+            assert o.usage_apply(uid, node, uuid, 0, mem, cores) == 0
+        ref = o.filter(pod, case["args"]["NodeNames"])
+        assert parity.compare([("filter", pod)], [ref], [out]) == [], case["name"]
+        o.close()
         e.close()
 
 

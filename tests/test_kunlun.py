@@ -264,3 +264,16 @@ def test_kunlun_gpu_parity(seed):
     got2 = [e.batch_get(i) for i in range(len(ops))]
     e.close()
     assert parity.compare(ops, ref, got2) == []
+
+
+@pytest.mark.gpu
+def test_general_path_in_streaming_mode(monkeypatch):
+    """HS_NO_RESIDENT=1 makes the decide loop take its streaming mode on a small inventory: there the general
+    evaluator's node list of a group is dealt to its 8 lanes (one thread evaluates AND commits a node).  Same stream,
+    same answers."""
+    import parity
+    monkeypatch.setenv("HS_NO_RESIDENT", "1")
+    cfg, nodes, ops = _kunlun_cluster(11, n_nodes=30, n_pods=500)
+    ref, ref_snap = parity.run_oracle(cfg, nodes, ops)
+    got, snap = parity.run_engine(cfg, nodes, ops, chunk=125)
+    assert parity.compare(ops, ref, got, ref_snap, snap) == []
