@@ -187,10 +187,10 @@ def algorithmic_bytes(ops, n_nodes):
 
 
 def decide_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum of ONE hs_decide_kernel launch, from the committed ncu --set full
-    capture (profiles/r01_decide_full_final.json); None when the summary is missing."""
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the decide kernel, from the committed ncu --set full
+    capture (profiles/r02_decide_fast_ncu_summary.json); None when the summary is missing."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_decide_full_final.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_decide_fast_ncu_summary.json")) as f:
             return int(json.load(f)["dram_bytes_per_launch"])
     except (OSError, KeyError, ValueError):
         return None
@@ -315,7 +315,8 @@ def run_ours(args):
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "traffic": decide_traffic(), "peak_source": peak_src,
-                     "kernel": "hs_decide_kernel",
+                     "kernel": "hs_decide_fast_kernel" if WORKLOAD in ("c1", "c2", "c3") else
+                               "hs_decide_fast_kernel, and hs_decide_kernel for the ranges that hold general-path pods",
                      "note": "algorithmic bytes = decisions x (N x 8 x 32 B + N x 128 B topology tile + nums x 16 B); "
                              "the inventory is L2/register resident, HBM evidence is the scan probe (profiles/)"},
     }
