@@ -234,6 +234,8 @@ struct hs_handle {
   double last_ms = 0;
   uint64_t launches = 0;
   int block = 256;          // threads per CTA of the decide kernel: 8 lanes per node
+  bool small_direct = false;    // this batch: results are written straight into the pinned host mirrors (device_begin)
+  bool no_small_direct = false; // HS_NO_SMALL_DIRECT=1: always copy results back (A/B of the single-call latency)
   bool no_fast = false;     // HS_NO_FAST=1: force the general evaluator (A/B testing of the two device paths)
   bool no_resident = false; // HS_NO_RESIDENT=1: force the streaming mode of the decide loop (tests: the lane-dealt general path on small inventories)
 
@@ -1083,6 +1085,7 @@ int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_ca
 // the current one (run_ops): device_begin sizes and clears the buffers for up to max_ops ops, device_range uploads the
 // records of ops [first, last) and runs them (draining the reason buffer and resuming as often as needed),
 // device_end brings the allocation rows and the collapsed deltas back.
+constexpr int kSmallDirectOps = 4;
 int device_begin(hs_handle* h, int max_ops, uint32_t alloc_bound) {
   int rc = flush_inventory(h);
   if (rc != HS_OK) return rc;
@@ -1111,7 +1114,11 @@ int device_begin(hs_handle* h, int max_ops, uint32_t alloc_bound) {
   }
   h->sync2_base = max_ops;
   if (h->have_cand) CUDA_OK(h, up(h, h->b_candpos.d, h->b_candpos.h, (size_t)n_nodes * sizeof(int32_t)));
-  CUDA_OK(h, cudaMemsetAsync(h->b_dec.d, 0xff, (size_t)max_ops * sizeof(DevDecision), h->stream));
+  // A handful of ops (one hs_filter): the kernel writes decisions, deltas, rows and counters straight into the pinned
+  // host mirrors (page-locked memory is device-addressable): no result copies, no device-side clearing of them
+  h->small_direct = max_ops <= kSmallDirectOps && h->shard_world <= 1 && !h->force_shard && !h->no_small_direct;
+  if (h->small_direct) memset(h->b_dec.h, 0xff, (size_t)max_ops * sizeof(DevDecision));
+  else CUDA_OK(h, cudaMemsetAsync(h->b_dec.d, 0xff, (size_t)max_ops * sizeof(DevDecision), h->stream));
   CUDA_OK(h, cudaMemsetAsync(h->b_best.d, 0, (size_t)max_ops * 2 * sizeof(OpSync), h->stream));   // [0,n): arg-best slots, [n,2n): quota barriers
   if (!h->quota_rows.empty())
     CUDA_OK(h, up(h, h->b_quota.d, h->b_quota.h, h->quota_rows.size() * 4 * sizeof(long long)));
@@ -1160,12 +1167,15 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
     CUDA_OK(h, up(h, h->b_entries.d + from.entries, h->b_entries.h + from.entries, (to.entries - from.entries) * sizeof(DevEntry)));
   if (to.uuid > from.uuid) CUDA_OK(h, up(h, h->b_uuid.d + from.uuid, h->b_uuid.h + from.uuid, (to.uuid - from.uuid) * sizeof(uint32_t)));
   if (to.rel > from.rel) CUDA_OK(h, up(h, h->b_rel.d + from.rel, h->b_rel.h + from.rel, (to.rel - from.rel) * sizeof(int4)));
-  CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
+  const bool direct = h->small_direct && with_rows;
+  if (direct) memset(h->b_counters.h, 0, 8 * sizeof(uint32_t));
+  else CUDA_OK(h, cudaMemsetAsync(h->b_counters.d, 0, 8 * sizeof(uint32_t), h->stream));
   int done = first;
   while (done < n_ops) {
     KernelArgs ka;
     build_kernel_args(h, ka, n_ops, alloc_cap);
     ka.op_begin = done;
+    if (direct) { ka.decisions = h->b_dec.h; ka.commit_delta = h->b_delta.h; ka.allocs = h->b_alloc.h; ka.counters = h->b_counters.h; }
     CUDA_OK(h, cudaEventRecord(h->ev0, h->stream));
     const bool fk = range_is_fast(h, done, n_ops);
     cudaError_t le = (cudaError_t)hs_launch_decide(&ka, fk ? h->grid_fast : grid, block, h->stream, fk ? 1 : 0);
@@ -1175,9 +1185,11 @@ int device_range(hs_handle* h, int first, int last, const StageMark& from, const
     // everything the launch produced comes back behind it on the stream, ONE synchronisation for all of it: counters,
     // the decisions of every op it may have reached (a launch normally runs to the end of its range), their collapsed
     // deltas and, for a pipelined chunk, its allocation rows
+    if (!direct) {
     CUDA_OK(h, down(h, h->b_counters.h, h->b_counters.d, 8 * sizeof(uint32_t)));
     CUDA_OK(h, down(h, h->b_dec.h + done, h->b_dec.d + done, (size_t)(n_ops - done) * sizeof(DevDecision)));
-    if (with_rows) {
+    }
+    if (with_rows && !direct) {
       CUDA_OK(h, down(h, h->b_delta.h + (size_t)done * HS_D, h->b_delta.d + (size_t)done * HS_D, (size_t)(n_ops - done) * HS_D * sizeof(int4)));
       if (alloc_to > alloc_from) CUDA_OK(h, down(h, h->b_alloc.h + alloc_from, h->b_alloc.d + alloc_from, (size_t)(alloc_to - alloc_from) * sizeof(DevAlloc)));
     }
@@ -2241,6 +2253,7 @@ hs_handle* hs_create(const hs_config* cfg) {
   const char* blk = getenv("HS_BLOCK");
   if (blk) { int b = atoi(blk); if (b >= 32 && b <= 512 && b % 32 == 0) h->block = b; }
   h->no_fast = getenv("HS_NO_FAST") != nullptr;
+  h->no_small_direct = getenv("HS_NO_SMALL_DIRECT") != nullptr;
   h->no_resident = getenv("HS_NO_RESIDENT") != nullptr;
   h->force_shard = getenv("HS_FORCE_SHARD") != nullptr;
   h->shard_use_nccl = getenv("HS_SHARD_NCCL") != nullptr;
