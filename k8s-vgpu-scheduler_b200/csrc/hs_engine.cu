@@ -960,6 +960,21 @@ inline uint32_t mig_dflags(uint32_t df, uint32_t occ, int bad) {
   return (bad == 0 && (df & DF_HEALTH_REG)) ? (df | DF_HEALTH) : (df & ~DF_HEALTH);
 }
 
+// A pod WITHOUT reservations joins (+1) or leaves (-1) the cache: it only moves the fail-closed count of the MIG GPUs it
+// has entries on (mig_pod_effect with an empty reservation list), so the mirror follows without walking the pod cache —
+// the case of every commit of a batch.
+void mig_apply_orphan(hs_handle* h, int slot, const PodRec& pr, int sign) {
+  const NodeSlot& ns = h->nodes[slot];
+  for (size_t d = 0; d < ns.devs.size() && d < (size_t)HS_D; d++) {
+    if (pr.n_ent[d] == 0 || ns.devs[d].mode != "mig") continue;
+    int4& v = h->h_dyn[inv_idx(slot, (int)d)];
+    const uint32_t df = (uint32_t)v.w;
+    int bad = (int)DF_BAD(df) + sign;
+    bad = bad < 0 ? 0 : bad;
+    v.w = (int)mig_dflags(df, DF_OCC(df), bad);
+  }
+}
+
 // Bring the node's dflags (host mirror) in line with the pod cache; true when something changed.
 bool mig_refresh(hs_handle* h, int slot) {
   NodeSlot& ns = h->nodes[slot];
@@ -1635,8 +1650,12 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
       uint8_t o[HS_D], b[HS_D], occ[HS_D]; int bad[HS_D];
       mig_pod_effect(h, h->nodes[it->second.node], it->second, o, b);
       released.insert(uid);
-      mig_node_state(h, it->second.node, &released, occ, bad);
-      for (int d = 0; d < HS_D; d++) rel[(size_t)p.rel_off + d].w = (int)((b[d] ? 1u : 0u) | 2u | ((uint32_t)occ[d] << 8));
+      if (it->second.mig.empty()) {      // no reservation: the pod only ever moved the fail-closed counts
+        for (int d = 0; d < HS_D; d++) rel[(size_t)p.rel_off + d].w = b[d] ? 1 : 0;
+      } else {
+        mig_node_state(h, it->second.node, &released, occ, bad);
+        for (int d = 0; d < HS_D; d++) rel[(size_t)p.rel_off + d].w = (int)((b[d] ? 1u : 0u) | 2u | ((uint32_t)occ[d] << 8));
+      }
       p.flags |= PF_REL_MIG;
     }
     {   // the same rows inside the op record (RelDelta over e0): the resident owner needs no second fetch
@@ -1681,19 +1700,21 @@ void absorb_results(hs_handle* h, int first, int last) {
       pr.ns = m.ns;
       quota_track(h, m.ns, dec.node, pr.delta, +1);
       h->pods[m.uid] = pr;
-      if (h->nodes[dec.node].has_mig) mig_refresh(h, dec.node);
+      if (h->nodes[dec.node].has_mig) mig_apply_orphan(h, dec.node, pr, +1);
     } else if (m.kind == OP_RELEASE) {
       const DevPod& p = h->b_pods.h[op];
       if (p.rel_node >= 0) {
         apply_host_delta(h, p.rel_node, h->b_rel.h + p.rel_off, -1);
         quota_track(h, m.ns, p.rel_node, h->b_rel.h + p.rel_off, -1);
         auto known = h->pods.find(m.uid);  // podManager.DelPod: only now, with the device's release done
+        bool full = (p.flags & PF_REL_MIG) != 0;
         if (known != h->pods.end()) {
           h->n_parked -= known->second.parked.size();
           if (!known->second.mig.empty()) h->n_mig_pods--;
+          else if (full) { mig_apply_orphan(h, p.rel_node, known->second, -1); full = false; }   // no reservation: the counts only
           h->pods.erase(known);
         }
-        if (p.flags & PF_REL_MIG) mig_refresh(h, p.rel_node);
+        if (full) mig_refresh(h, p.rel_node);
       } else {
         auto it = h->pods.find(m.uid);
         if (it != h->pods.end()) {
@@ -1701,8 +1722,8 @@ void absorb_results(hs_handle* h, int first, int last) {
           quota_track(h, it->second.ns, it->second.node, it->second.delta, -1);
           h->n_parked -= it->second.parked.size();
           const int rel_node = it->second.node;
+          if (h->nodes[rel_node].has_mig) mig_apply_orphan(h, rel_node, it->second, -1);   // committed in this batch: no reservation yet
           h->pods.erase(it);
-          if (h->nodes[rel_node].has_mig) mig_refresh(h, rel_node);
         }
       }
     }
