@@ -211,6 +211,37 @@ func (e *Engine) UpsertNode(info *device.NodeInfo, cordon string, hasCordon bool
 		if len(d.DevicePairScore.Scores) > 0 {
 			anyPair = true
 		}
+		if profiles, ok := d.CustomInfo["profiles"]; ok { // enflame shared vGCU: CustomInfo of GetNodeDevices (enflame/device.go:235-252)
+			ef := (*C.hs_enflame_info)(a.alloc(1, unsafe.Sizeof(C.hs_enflame_info{})))
+			ef.minor = a.str(fmt.Sprint(d.CustomInfo["minor"]))
+			ef.index = a.str(fmt.Sprint(d.CustomInfo["index"]))
+			if ms, ok := d.CustomInfo["maxSlice"].(int); ok {
+				ef.max_slice = C.int32_t(ms)
+			}
+			var names, ids []string
+			switch m := profiles.(type) {
+			case map[string]string:
+				for k, v := range m {
+					names, ids = append(names, k), append(ids, v)
+				}
+			case map[string]any:
+				for k, v := range m {
+					if sv, ok := v.(string); ok {
+						names, ids = append(names, k), append(ids, sv)
+					}
+				}
+			}
+			if len(names) > 0 {
+				kv := (*[1 << 8]C.hs_kv)(a.alloc(uintptr(len(names)), unsafe.Sizeof(C.hs_kv{})))
+				for k := range names {
+					kv[k].key = a.str(names[k])
+					kv[k].value = a.str(ids[k])
+				}
+				ef.profiles = &kv[0]
+				ef.n_profiles = C.uint32_t(len(names))
+			}
+			arr[i].enflame = ef
+		}
 		if d.Mode == "mig" && len(d.MIGProfiles) > 0 { // DeviceInfo.MIGProfiles, devices.go:141: what dynamic MIG selects from
 			profs := (*[1 << 8]C.hs_mig_profile)(a.alloc(uintptr(len(d.MIGProfiles)), unsafe.Sizeof(C.hs_mig_profile{})))
 			for k, mp := range d.MIGProfiles {
@@ -366,7 +397,14 @@ func buildPod(a *arena, pod *corev1.Pod, reqs device.PodDeviceRequests) *C.hs_po
 	// device.Resourcereqs(pod) (devices.go:639-691): one map per container, init containers first
 	if n := len(reqs); n > 0 {
 		cs := (*[1 << 10]C.hs_container)(a.alloc(uintptr(n), unsafe.Sizeof(C.hs_container{})))
+		nInit := len(pod.Spec.InitContainers)
 		for ci, m := range reqs {
+			// Container.Name by position: enflame's assigned-containers annotation is keyed by it (enflame/device.go:692-705)
+			if ci < nInit {
+				cs[ci].name = a.str(pod.Spec.InitContainers[ci].Name)
+			} else if ci-nInit < len(pod.Spec.Containers) {
+				cs[ci].name = a.str(pod.Spec.Containers[ci-nInit].Name)
+			}
 			if len(m) == 0 {
 				continue
 			}

@@ -85,6 +85,21 @@ typedef struct hs_mig_profile {
   uint32_t                n_placements;
 } hs_mig_profile;
 
+typedef struct hs_kv {
+  const char* key;
+  const char* value;
+} hs_kv;
+
+/* CustomInfo of one enflame shared-vGCU ("DRS") device as GetNodeDevices builds it (enflame/device.go:235-252):
+ * minor, index, the node's profile map (profile name such as "3g.20gb" -> profile id) and maxSlice.               */
+typedef struct hs_enflame_info {
+  const char*  minor;
+  const char*  index;
+  int32_t      max_slice;
+  const hs_kv* profiles;
+  uint32_t     n_profiles;
+} hs_enflame_info;
+
 /* device.DeviceInfo (pkg/device/devices.go:127-144) as the register path hands
  * it to nodeManager.addNode (pkg/scheduler/nodes.go:76).                    */
 typedef struct hs_device_info {
@@ -101,6 +116,7 @@ typedef struct hs_device_info {
   int32_t     network_id;/* CustomInfo["NetworkID"] (Ascend), -1 = absent */
   const hs_mig_profile* mig_profiles;   /* DeviceInfo.MIGProfiles (devices.go:141); read for mode "mig" only */
   uint32_t    n_mig_profiles;
+  const hs_enflame_info* enflame;       /* HS_FIT_ENFLAME_VGCU devices only; NULL = no CustomInfo                */
 } hs_device_info;
 
 /* device.NodeInfo (pkg/device/devices.go:170-174) plus the node annotations the
@@ -139,12 +155,9 @@ typedef struct hs_container_request {
 typedef struct hs_container {
   const hs_container_request* reqs;
   uint32_t                    n_reqs;
+  const char*                 name;   /* Container.Name; read by the one PatchAnnotations that keys on it (enflame's
+                                       * assigned-containers, enflame/device.go:268-297); NULL = "container-<index>"  */
 } hs_container;
-
-typedef struct hs_kv {
-  const char* key;
-  const char* value;
-} hs_kv;
 
 /* The parts of *corev1.Pod that Filter reads: UID, namespace, annotations,
  * and Resourcereqs(pod) (devices.go:639-691): init containers first.       */
@@ -292,7 +305,21 @@ enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
         * request's Memreq / Coresreq, usage is added in full, ScoreNode is 0, both annotation keys are written.  Failure:
         * under mutex the number of in-use cards that would otherwise fit ("ExclusiveDeviceAllocateConflict"), else the
         * cards a uuid list turned away, else "1/n NumaNotFit".                                                          */
-       HS_FIT_KUNLUN_VXPU = 9 };
+       HS_FIT_KUNLUN_VXPU = 9,
+       /* enflame shared vGCU, type "Enflame" (pkg/device/enflame/device.go:382-478).  Every request is first turned into
+        * ONE profile of the node (selectProfileByRequest, :498-531): the candidates are the profiles the node's devices
+        * advertise (hs_enflame_info; "<slices>g.<GB>gb"), sorted by (slices, GB) — equal ones in ascending name — with a core
+        * share of ceil(slices * 100 / maxSlice); MemPercentagereq 0 ("direct", a enflame.com/drs-gcu request) takes the
+        * profile whose slice count equals Memreq, anything else the first profile that covers the memory (values above
+        * twice the largest profile are read as MiB and rounded up to GB) and the core share asked.  No profile:
+        * "1/n ModeNotFit".  Then health, type, uuid (enflame.com/use-gpuuuid / nouse-gpuuuid), slots, mutex, the
+        * profile's memory (GB * 1024) and core share (when Totalcore > 0); the pick records those and the profile;
+        * AddResourceUsage adds the slice count to Used.  hs_alloc_entry.mig_profile carries the profile name and
+        * mig_start its slice count.  Annotations (:254-300): the allocated key, enflame.com/gcu-assigned = "false",
+        * gcu-assigned-time (returned empty), gcu-assigned-index / -id / -minor and gcu-request-size of the first
+        * container with a device, assigned-containers = {"<container name>": {"allocated":false,"request":<slices>,
+        * "profileID":…,"profileName":…}} (hs_container.name).                                                          */
+       HS_FIT_ENFLAME_VGCU = 10 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */
@@ -434,6 +461,9 @@ enum { HS_REQ_NVIDIA = 0, HS_REQ_DCU = 1, HS_REQ_MLU = 2, HS_REQ_ASCEND = 3,
        HS_REQ_METAX = 9,      /* metax/device.go:134-154: Memreq 0, MemPercentagereq 100, Coresreq 100            */
        HS_REQ_KUNLUN_VXPU = 11, /* kunlun/vdevice.go:173-213: count + memory trimmed up to 24576 / 49152 / 98304 MiB, cores =
                                * the memory's share of a card in percent; no memory = the whole card                 */
+       HS_REQ_ENFLAME = 12,   /* enflame/device.go:322-366: count_name (enflame.com/drs-gcu) > 0 = a direct slice request (Nums 1,
+                               * Memreq = the count, MemPercentagereq 0); else memory_name / cores_name by spec (Nums 1,
+                               * Memreq, Coresreq, MemPercentagereq -1); Quantity.Value() of Limits, then Requests        */
        HS_REQ_NEURON = 10     /* awsneuron/device.go:287-334: by device (count_name) or by NeuronCore (cores_name, split
                                * over devices); default_cores = the vendor object's coresPerAWSNeuron                */
 };
@@ -467,6 +497,9 @@ enum { HS_REG_CSV = 0,    /* device.DecodeNodeDevices  (pkg/device/devices.go:31
                                       * .scores values or NULL (hs_node_register hands them to hs_node_info)            */
        HS_REG_CAPACITY_KUNLUN = 6,   /* kunlun/device.go:64-91: capacity_cores = the XPU count, <node>-kunlun-<i>, Count 100,
                                       * 98304 MiB, the upper half of the cards on NUMA 1                                */
+       HS_REG_ENFLAME_DRS = 7,       /* enflame/device.go:198-252: `annotation` = the node's enflame.com/gcu-drs-capacity JSON
+                                      * {"devices":[{"index","minor","capacity"}],"profiles":{name:id}}; <node>-enflame-drs-<i>,
+                                      * Count = capacity, Devmem = the largest profile's GB * 1024, Devcore 100            */
        HS_REG_CAPACITY_NEURON = 5    /* awsneuron/device.go:156-198: capacity_cores = the DEVICE count, capacity_memory = the
                                       * node's total core count, capacity_aux = the vendor object's coresPerAWSNeuron so far
                                       * (0 = unknown: total / count, which the caller then keeps), `annotation` = the node's

@@ -18,6 +18,15 @@ REASONS = [
 ]
 
 
+class hs_kv(C.Structure):
+    _fields_ = [("key", C.c_char_p), ("value", C.c_char_p)]
+
+
+class hs_enflame_info(C.Structure):
+    _fields_ = [("minor", C.c_char_p), ("index", C.c_char_p), ("max_slice", C.c_int32),
+                ("profiles", C.POINTER(hs_kv)), ("n_profiles", C.c_uint32)]
+
+
 class hs_mig_placement(C.Structure):
     _fields_ = [("start", C.c_uint32), ("size", C.c_uint32)]
 
@@ -35,7 +44,21 @@ class hs_device_info(C.Structure):
     _fields_ = [("id", C.c_char_p), ("index", C.c_uint32), ("count", C.c_int32), ("devmem", C.c_int32),
                 ("devcore", C.c_int32), ("type", C.c_char_p), ("numa", C.c_int32), ("mode", C.c_char_p),
                 ("health", C.c_uint8), ("vendor", C.c_char_p), ("network_id", C.c_int32),
-                ("mig_profiles", C.POINTER(hs_mig_profile)), ("n_mig_profiles", C.c_uint32)]
+                ("mig_profiles", C.POINTER(hs_mig_profile)), ("n_mig_profiles", C.c_uint32),
+                ("enflame", C.POINTER(hs_enflame_info))]
+
+
+def build_enflame_info(info, keep):
+    """{"minor", "index", "max_slice", "profiles": {name: id}} -> POINTER(hs_enflame_info) or None"""
+    if not info:
+        return None
+    profs = list((info.get("profiles") or {}).items())
+    kv = (hs_kv * max(1, len(profs)))()
+    for i, (k, v) in enumerate(profs):
+        kv[i] = hs_kv(_b(k), _b(v))
+    e = hs_enflame_info(_b(info.get("minor", "")), _b(info.get("index", "")), int(info.get("max_slice", 0)), kv, len(profs))
+    keep += [kv, e]
+    return C.pointer(e)
 
 
 def build_mig_profiles(profiles, keep):
@@ -87,7 +110,7 @@ class hs_sim_node(C.Structure):
 
 
 HS_REG_CSV, HS_REG_JSON, HS_REG_CAPACITY_MLU, HS_REG_CAPACITY_MTHREADS, HS_REG_CAPACITY_METAX, HS_REG_CAPACITY_NEURON = 0, 1, 2, 3, 4, 5
-HS_REG_CAPACITY_KUNLUN = 6
+HS_REG_CAPACITY_KUNLUN, HS_REG_ENFLAME_DRS = 6, 7
 
 
 class hs_container_request(C.Structure):
@@ -96,11 +119,7 @@ class hs_container_request(C.Structure):
 
 
 class hs_container(C.Structure):
-    _fields_ = [("reqs", C.POINTER(hs_container_request)), ("n_reqs", C.c_uint32)]
-
-
-class hs_kv(C.Structure):
-    _fields_ = [("key", C.c_char_p), ("value", C.c_char_p)]
+    _fields_ = [("reqs", C.POINTER(hs_container_request)), ("n_reqs", C.c_uint32), ("name", C.c_char_p)]
 
 
 class hs_pod(C.Structure):
@@ -159,7 +178,7 @@ class hs_vendor_resources(C.Structure):
 
 HS_REQ_NVIDIA, HS_REQ_DCU, HS_REQ_MLU, HS_REQ_ASCEND = 0, 1, 2, 3
 HS_REQ_ILUVATAR, HS_REQ_COUNT, HS_REQ_AMD, HS_REQ_MTHREADS, HS_REQ_WHOLE_CARD, HS_REQ_METAX, HS_REQ_NEURON = 4, 5, 6, 7, 8, 9, 10
-HS_REQ_KUNLUN_VXPU = 11
+HS_REQ_KUNLUN_VXPU, HS_REQ_ENFLAME = 11, 12
 
 
 class hs_vendor_config(C.Structure):
@@ -169,7 +188,7 @@ class hs_vendor_config(C.Structure):
 
 
 HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD, HS_FIT_METAX, HS_FIT_NEURON, HS_FIT_VASTAI = 0, 1, 2, 3, 4, 5, 6, 7
-HS_FIT_KUNLUN, HS_FIT_KUNLUN_VXPU = 8, 9
+HS_FIT_KUNLUN, HS_FIT_KUNLUN_VXPU, HS_FIT_ENFLAME_VGCU = 8, 9, 10
 
 # The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
 # (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
@@ -197,6 +216,8 @@ DEFAULT_VENDORS = [
     # kunlun whole XPUs (kunlun/device.go:32-56): SupportDevices only; the second uuid pair (baidu.com/...) is fixed in the Fit
     ("kunlun", HS_FIT_KUNLUN, "hami.io/use-xpu-uuid", "hami.io/no-use-xpu-uuid", None, "hami.io/kunlun-allocated"),
     # kunlun shared XPUs (kunlun/vdevice.go:34-63)
+    # enflame shared vGCU (enflame/device.go:38-46,86-104): SupportDevices only
+    ("Enflame", HS_FIT_ENFLAME_VGCU, "enflame.com/use-gpuuuid", "enflame.com/nouse-gpuuuid", None, "hami.io/enflame-vgpu-devices-allocated"),
     ("XPU", HS_FIT_KUNLUN_VXPU, "hami.io/use-xpu-uuid", "hami.io/no-use-xpu-uuid", "hami.io/xpu-devices-to-allocate",
      "hami.io/xpu-devices-allocated"),
 ]
@@ -271,7 +292,7 @@ def build_node(node):
         arr[i] = hs_device_info(_b(d["id"]), d.get("index", i), d.get("count", 0), d.get("devmem", 0),
                                 d.get("devcore", 0), _b(d.get("type", "")), d.get("numa", 0), _b(d.get("mode", "")),
                                 1 if d.get("health", True) else 0, _b(d.get("vendor", "NVIDIA")),
-                                d.get("network_id", -1), mp, nmp)
+                                d.get("network_id", -1), mp, nmp, build_enflame_info(d.get("enflame"), keep))
     ps = None
     if node.get("pair_scores") is not None:
         n = len(devs)
@@ -301,7 +322,8 @@ def build_pod(pod):
             rarr[j] = hs_container_request(_b(r.get("key", r["type"])), _b(r["type"]), r.get("nums", 0),
                                            r.get("memreq", 0), r.get("mempct", 0), r.get("coresreq", 0))
         keep.append(rarr)
-        carr[i] = hs_container(rarr, len(reqs))
+        names = pod.get("container_names") or []
+        carr[i] = hs_container(rarr, len(reqs), _b(names[i]) if i < len(names) and names[i] is not None else None)
     keep += [kv, carr]
     p = hs_pod(_b(pod.get("uid", pod.get("name", ""))), _b(pod.get("ns", "default")), _b(pod.get("name", "")),
                kv, len(annos), carr, len(ctrs), pod.get("n_init", 0))

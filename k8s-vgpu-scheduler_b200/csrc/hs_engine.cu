@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <array>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <deque>
@@ -124,13 +125,20 @@ struct DevSlot {
   int32_t count = 0, devmem = 0, devcore = 0, numa = 0, network_id = -1;
   bool health = true;
   int type_id = 0, mode_id = 0, vendor_id = 0;
-  int mig_geom = 0;         // index into hs_handle::mig_geoms for a GPU in MIG mode (0 = the empty geometry)
+  int mig_geom = 0;         // index into hs_handle::mig_geoms for a GPU in MIG mode (0 = the empty geometry); enflame: the node's profile table
+  std::string enf_minor, enf_index;                               // enflame CustomInfo["minor"] / ["index"]
+  std::vector<std::pair<std::string, std::string>> enf_profiles;  // … ["profiles"]
+  int enf_max_slice = 0;                                          // … ["maxSlice"]
 };
 
 // One distinct MigProfiles list (device.MigProfile, devices.go:79-90) and what the device needs of it (MigGeom)
 struct MigGeomHost {
   struct Prof { std::string name; int32_t memory_mb, core; uint32_t slice_count; std::vector<std::pair<uint32_t, uint32_t>> placements; };
   std::vector<Prof> profiles;   // as registered
+  // enflame: the node's DRS profile candidates in selectProfileByRequest's order (enflame/device.go:567-619)
+  struct Enf { std::string name, id; long long size, mem_gb, core; };
+  std::vector<Enf> enf;
+  bool enflame = false;
   MigGeom dev;
 };
 struct MigRes { std::string uuid, profile; uint32_t start = 0, size = 0; };   // one entry of hami.io/vgpu-mig-allocations
@@ -163,6 +171,7 @@ struct VendorInfo {
   bool metax = false;       // metax whole GPUs: mthreads' gates without uuid lists + ScoreNode from the node's annotations (EF_METAX)
   int fit_kind = 0;         // HS_FIT_* as registered (hs_filter_simulate hands it on to the child handle)
   bool vastai = false;      // vastai: count-only gates + die mode (EF_VASTAI)
+  bool enflame = false;     // enflame shared vGCU: DRS profile selection per request (EF_ENFLAME)
   bool kunlun = false;      // kunlun whole XPUs: graghSelect, slot-only usage, wing ScoreNode (EF_KUNLUN)
   bool vxpu = false;        // … the shared "XPU" type on the same graghSelect (EF_KUNLUN | EF_VXPU)
   bool amd = false;         // amd's Fit: whole-card defaults, per-device core share, picks carry the device's type (EF_AMD)
@@ -189,6 +198,7 @@ struct OpMeta {           // host-side memory of one op of the current batch
   int kind = OP_NOP;      // OP_FILTER / OP_RELEASE / OP_NOP
   int status = HS_OK;     // compile-time verdict: HS_PASSTHROUGH / HS_ERR_*
   std::string uid, vnpu_mode, ns;
+  std::vector<std::string> ctr_names;   // Container.Name by position (enflame's assigned-containers annotation)
   int n_ctr = 0, n_init = 0;
   std::vector<EntryMeta> entries;
   std::vector<uint8_t> ctr_begin;
@@ -483,7 +493,7 @@ inline cudaError_t down_sync(hs_handle* h, void* dst, const void* src, size_t by
 }
 
 int flush_inventory(hs_handle* h) {
-  if (h->has_mig && h->mig_tab_uploaded != h->mig_geoms.size()) {      // the MIG geometry table: 16 x 272 B, rewritten when a new one appears
+  if (h->mig_tab_uploaded != h->mig_geoms.size()) {      // the MIG geometry table: 16 x 272 B, rewritten when a new one appears
     if (!h->d_mig_tab) CUDA_OK(h, cudaMalloc(&h->d_mig_tab, 16 * sizeof(MigGeom)));
     std::vector<MigGeom> tab(16);
     memset(tab.data(), 0, 16 * sizeof(MigGeom));
@@ -697,6 +707,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     }
     p.ctr_begin[ci] = (uint8_t)c.entries.size();
     c.meta.ctr_begin[ci] = (uint8_t)c.entries.size();
+    c.meta.ctr_names.push_back(pod->containers[ci].name ? pod->containers[ci].name : "container-" + std::to_string(ci));
     for (auto& kv : m) {
       const hs_container_request* q = kv.second;
       if (c.entries.size() >= HS_MAX_E) { h->err = "pod has more request entries than HS_MAX_REQS_PER_POD"; return HS_ERR_UNSUPPORTED; }
@@ -715,6 +726,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       if (v && v->neuron) e.flags |= EF_NEURON;
       if (v && v->whole_card) e.flags |= EF_WHOLE_CARD;
       if (v && v->kunlun) e.flags |= EF_KUNLUN;
+      if (v && v->enflame) e.flags |= EF_ENFLAME;
       if (v && v->vxpu) e.flags |= EF_VXPU;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
@@ -783,7 +795,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     // pairing stays with the general evaluator
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
               !(e.flags & EF_ASCEND910C)) ? 1 : 0;
-    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX | EF_NEURON | EF_KUNLUN))) p.fast = 0;
+    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX | EF_NEURON | EF_KUNLUN | EF_ENFLAME))) p.fast = 0;
   }
   if (h->has_mig)       // dynamic MIG lives in the general evaluator: every NVIDIA request of a handle that holds a GPU in MIG mode
     for (const DevEntry& e : c.entries) {
@@ -888,6 +900,96 @@ int intern_geom(hs_handle* h, const hs_mig_profile* profiles, uint32_t n, std::s
     mc.mem = cp.memory_mb; mc.core = (int16_t)cp.core; mc.prof = (uint8_t)order[c];
     mc.n_place = (uint8_t)pl.size();
     for (size_t j = 0; j < pl.size(); j++) mc.place[j] = (uint8_t)((pl[j].first << 4) | pl[j].second);
+  }
+  h->mig_geoms.push_back(g);
+  return (int)h->mig_geoms.size() - 1;
+}
+
+// strconv.Atoi on a profile name part (decimal, optional sign); false = not a number
+static bool enf_atoi(const std::string& t, long long& out) {
+  if (t.empty()) return false;
+  size_t i = 0;
+  bool neg = false;
+  if (t[0] == '+' || t[0] == '-') { neg = t[0] == '-'; i = 1; }
+  if (i >= t.size()) return false;
+  unsigned long long v = 0;
+  for (; i < t.size(); i++) {
+    if (t[i] < '0' || t[i] > '9') return false;
+    if (v > (0x7fffffffffffffffULL - (unsigned)(t[i] - '0')) / 10) return false;      // out of int64 range: Atoi errors
+    v = v * 10 + (unsigned)(t[i] - '0');
+  }
+  out = neg ? -(long long)v : (long long)v;
+  return true;
+}
+// parseProfile, enflame/device.go:621-643: "<slices>g.<GB>gb"
+static void enf_parse_profile(const std::string& name, long long& size, long long& mem_gb) {
+  size = 0; mem_gb = 0;
+  std::string n = trimSpace(name);
+  for (auto& c : n) if (c >= 'A' && c <= 'Z') c = (char)(c + 32);
+  std::vector<std::string> parts;
+  size_t pos = 0;
+  for (;;) { size_t q = n.find('.', pos); if (q == std::string::npos) { parts.push_back(n.substr(pos)); break; } parts.push_back(n.substr(pos, q - pos)); pos = q + 1; }
+  if (parts.size() < 2) return;
+  std::string sp = trimSpace(parts[0]);
+  if (!sp.empty() && sp.back() == 'g') sp.pop_back();
+  long long sz;
+  if (!enf_atoi(sp, sz)) return;
+  size = sz;
+  std::string mp = trimSpace(parts[1]);
+  if (mp.size() >= 2 && mp.compare(mp.size() - 2, 2, "gb") == 0) mp.erase(mp.size() - 2);
+  long long mg;
+  if (!enf_atoi(mp, mg)) return;
+  mem_gb = mg;
+}
+// The node's candidate table (collectDRSProfiles): every profile name the node's vGCU devices advertise that parses to a
+// positive slice count and memory, a later device's id winning, core share = ceil(slices * 100 / maxSlice), sorted by
+// (slices, GB) — equal ones in ascending name (the reference iterates a Go map there).
+int intern_enflame(hs_handle* h, const std::vector<DevSlot*>& devs, std::string& err) {
+  long long maxSlice = 0;
+  for (auto* d : devs) if (d->enf_max_slice > maxSlice) maxSlice = d->enf_max_slice;
+  if (maxSlice <= 0)
+    for (auto* d : devs)
+      for (auto& kv : d->enf_profiles) { long long s, m; enf_parse_profile(kv.first, s, m); if (s > maxSlice) maxSlice = s; }
+  MigGeomHost g;
+  g.enflame = true;
+  memset(&g.dev, 0, sizeof g.dev);
+  if (maxSlice > 0) {
+    std::map<std::string, MigGeomHost::Enf> seen;
+    for (auto* d : devs)
+      for (auto& kv : d->enf_profiles) {
+        long long s, m;
+        enf_parse_profile(kv.first, s, m);
+        if (s <= 0 || m <= 0) continue;
+        seen[kv.first] = MigGeomHost::Enf{kv.first, kv.second, s, m, (long long)std::ceil((double)s * 100 / (double)maxSlice)};
+      }
+    for (auto& kv : seen) g.enf.push_back(kv.second);
+    std::stable_sort(g.enf.begin(), g.enf.end(), [](const MigGeomHost::Enf& a, const MigGeomHost::Enf& b) {
+      if (a.size == b.size) return a.mem_gb < b.mem_gb;
+      return a.size < b.size;
+    });
+  }
+  if (g.enf.size() > 16) { err = "an enflame node advertises more than 16 usable DRS profiles"; return -1; }
+  for (size_t k = 0; k < h->mig_geoms.size(); k++) {
+    const auto& o = h->mig_geoms[k];
+    if (!o.enflame || o.enf.size() != g.enf.size()) continue;
+    bool same = true;
+    for (size_t i = 0; i < o.enf.size() && same; i++)
+      same = o.enf[i].name == g.enf[i].name && o.enf[i].id == g.enf[i].id && o.enf[i].core == g.enf[i].core;
+    if (same) return (int)k;
+  }
+  if (h->mig_geoms.size() >= 16) { err = "more than 15 distinct MIG geometries / enflame profile tables on one handle"; return -1; }
+  g.dev.n_cand = (uint32_t)g.enf.size();
+  for (size_t c = 0; c < g.enf.size(); c++) {
+    const auto& p = g.enf[c];
+    MigCand& mc = g.dev.cand[c];
+    // the reference turns these into "1/n ModeNotFit" when selected (enflame/device.go:393-408)
+    if (p.core > 32767) { err = "enflame profile core share outside the engine's int16 (slice count far above maxSlice)"; return -1; }
+    const bool valid = p.size <= 2147483647LL && p.mem_gb <= 2147483647LL / 1024;
+    mc.mem = valid ? (int32_t)(p.mem_gb * 1024) : -1;
+    mc.core = (int16_t)(p.core > 32767 ? 32767 : p.core);
+    mc.prof = (uint8_t)c;
+    const int32_t sz = (int32_t)std::min<long long>(p.size, 2147483647LL), gb = (int32_t)std::min<long long>(p.mem_gb, 2147483647LL);
+    for (int b = 0; b < 4; b++) { mc.place[b] = (uint8_t)((uint32_t)sz >> (8 * b)); mc.place[4 + b] = (uint8_t)((uint32_t)gb >> (8 * b)); }
   }
   h->mig_geoms.push_back(g);
   return (int)h->mig_geoms.size() - 1;
@@ -1064,7 +1166,7 @@ const std::string& fail_string_slow(hs_handle* h, const DevFail& f) {
 int build_kernel_args(hs_handle* h, KernelArgs& ka, int n_ops, uint32_t alloc_cap) {
   memset(&ka, 0, sizeof ka);
   ka.dyn = h->d_dyn; ka.stat = h->d_stat; ka.node_flags = h->d_flags; ka.node_tot = h->d_tot; ka.pair = h->d_pair;
-  ka.mig_tab = h->has_mig ? h->d_mig_tab : nullptr;
+  ka.mig_tab = h->mig_geoms.empty() ? nullptr : h->d_mig_tab;
   ka.no_resident = h->no_resident ? 1 : 0;
   ka.n_nodes = (int)((h->nodes.size() + HS_TILE - 1) / HS_TILE * HS_TILE);
   ka.cand_pos = h->have_cand ? h->b_candpos.d : nullptr;
@@ -1420,7 +1522,14 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
       const EntryMeta& em = m.entries[AL_ENTRY(a)];
       const DevSlot& ds = ns.devs[AL_DEV(a)];
       hs_alloc_entry row{0, em.type.c_str(), ds.uuid.c_str(), (int32_t)ds.index, a.usedmem, (int32_t)a.usedcores, nullptr, 0, 0};
-      if (AL_MIG(a) && ds.mig_geom > 0 && (size_t)ds.mig_geom < h->mig_geoms.size()) {
+      if (AL_MIG(a) && ds.mig_geom > 0 && (size_t)ds.mig_geom < h->mig_geoms.size() && h->mig_geoms[ds.mig_geom].enflame) {
+        // the DRS profile the enflame Fit chose (CustomInfo["profileName"] / ["drsSlice"], enflame/device.go:452-460)
+        const MigGeomHost& g = h->mig_geoms[ds.mig_geom];
+        if ((size_t)AL_MIG_CAND(a) < g.enf.size()) {
+          row.mig_profile = g.enf[AL_MIG_CAND(a)].name.c_str();
+          row.mig_start = (uint32_t)g.enf[AL_MIG_CAND(a)].size;
+        }
+      } else if (AL_MIG(a) && ds.mig_geom > 0 && (size_t)ds.mig_geom < h->mig_geoms.size()) {
         // CustomInfo["migProfile"] / ["migPlacement"] of the pick (nvidia/device.go:653-657)
         const MigGeomHost& g = h->mig_geoms[ds.mig_geom];
         const MigCand& mc = g.dev.cand[AL_MIG_CAND(a)];
@@ -1504,6 +1613,44 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
           annos["mthreads.com/gpu-index"] = value;
           annos["mthreads.com/predicate-time"] = "";
           annos["mthreads.com/predicate-node"] = ns.name;
+        }
+        continue;
+      }
+      if (v.enflame) {
+        // enflame/device.go:254-300: the allocated key, gcu-assigned, the (blanked) time, the first container's index /
+        // minor / slice count and assigned-containers keyed by container name
+        annos[v.allocated] = s;
+        annos["enflame.com/gcu-assigned"] = "false";
+        annos["enflame.com/gcu-assigned-time"] = "";
+        std::map<std::string, std::string> assigned;
+        for (size_t c = 0; c < it->second.size(); c++) {
+          if (it->second[c].empty()) continue;
+          const hs_alloc_entry* chosen = it->second[c][0];
+          const int slice = chosen->mig_start == 0 ? 1 : (int)chosen->mig_start;
+          std::string profile_id, minor, index;
+          for (const auto& d : ns.devs) {
+            if (d.uuid != chosen->uuid) continue;
+            minor = d.enf_minor; index = d.enf_index;
+            if (d.mig_geom > 0 && (size_t)d.mig_geom < h->mig_geoms.size() && chosen->mig_profile)
+              for (const auto& p : h->mig_geoms[d.mig_geom].enf) if (p.name == chosen->mig_profile) profile_id = p.id;
+            break;
+          }
+          const std::string name = c < m.ctr_names.size() ? m.ctr_names[c] : "container-" + std::to_string(c);
+          std::string o = "{\"allocated\":false,\"request\":" + std::to_string(slice);
+          if (!profile_id.empty()) o += ",\"profileID\":" + json_string(profile_id.c_str());
+          if (chosen->mig_profile && chosen->mig_profile[0]) o += ",\"profileName\":" + json_string(chosen->mig_profile);
+          assigned[name] = o + "}";
+          if (!annos.count("enflame.com/gcu-assigned-index") && !index.empty()) {
+            annos["enflame.com/gcu-assigned-index"] = index;
+            annos["enflame.com/gcu-assigned-id"] = index;
+          }
+          if (!annos.count("enflame.com/gcu-assigned-minor") && !minor.empty()) annos["enflame.com/gcu-assigned-minor"] = minor;
+          if (!annos.count("enflame.com/gcu-request-size") && slice > 0) annos["enflame.com/gcu-request-size"] = std::to_string(slice);
+        }
+        if (!assigned.empty()) {
+          std::string payload = "{";
+          for (auto& kv : assigned) { if (payload.size() > 1) payload += ","; payload += json_string(kv.first.c_str()) + ":" + kv.second; }
+          annos["assigned-containers"] = payload + "}";
         }
         continue;
       }
@@ -2260,6 +2407,7 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.whole_card = vc.fit_kind == HS_FIT_WHOLE_CARD;
       v.metax = vc.fit_kind == HS_FIT_METAX;
       v.neuron = vc.fit_kind == HS_FIT_NEURON;
+      v.enflame = vc.fit_kind == HS_FIT_ENFLAME_VGCU;
       v.kunlun = vc.fit_kind == HS_FIT_KUNLUN || vc.fit_kind == HS_FIT_KUNLUN_VXPU;
       v.vxpu = vc.fit_kind == HS_FIT_KUNLUN_VXPU;
       if (v.metax) { v.use_uuid.clear(); v.nouse_uuid.clear(); }   // checkUUID is constant true (metax/device.go:124-126)
@@ -2362,7 +2510,24 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
     if (s.vendor_id != HV_NONE && h->vendors[s.vendor_id].neuron && (s.devcore > 32767 || s.devcore < 0)) {
       h->err = "AWS Neuron core mask outside the engine's int16 allocation row"; return HS_ERR_UNSUPPORTED;
     }
+    if (d.enflame) {
+      s.enf_minor = d.enflame->minor ? d.enflame->minor : ""; s.enf_index = d.enflame->index ? d.enflame->index : "";
+      s.enf_max_slice = d.enflame->max_slice;
+      for (uint32_t k = 0; k < d.enflame->n_profiles; k++)
+        s.enf_profiles.emplace_back(d.enflame->profiles[k].key ? d.enflame->profiles[k].key : "", d.enflame->profiles[k].value ? d.enflame->profiles[k].value : "");
+    }
     devs.push_back(s);
+  }
+  {   // enflame: ONE profile table per node, collected over its vGCU devices (collectDRSProfiles, enflame/device.go:567-619)
+    std::vector<DevSlot*> enf;
+    for (auto& s : devs) if (s.vendor_id != HV_NONE && h->vendors[s.vendor_id].enflame) enf.push_back(&s);
+    if (!enf.empty()) {
+      if (h->shard_world > 1) { h->err = "enflame vGCU nodes are not supported on the sharded (multi-GPU) path"; return HS_ERR_UNSUPPORTED; }
+      if (h->mig_geoms.empty()) { std::string e; intern_geom(h, nullptr, 0, e); }
+      const int g = intern_enflame(h, enf, h->err);
+      if (g < 0) return HS_ERR_UNSUPPORTED;
+      for (auto* s : enf) s->mig_geom = g;
+    }
   }
   // canonical rule 5: vendors in sorted key order, registration order inside a vendor
   std::vector<int> perm(devs.size());

@@ -246,6 +246,38 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
     out.fkind = FK_HIST;
     out.fcards = (uint32_t)cnt;
   }
+  if (e.flags & EF_ENFLAME) {
+    // enflame shared vGCU, enflame/device.go:382-478: the request becomes one profile of the node, then the gates
+    int sel = -1;
+    if (cnt > 0 && ka.mig_tab != nullptr) sel = hs_enf_select(ka.mig_tab[PK_GEOM(w.packed[td[0]])], e.memreq, e.mempct, e.coresreq);
+    const MigCand* pc = sel >= 0 ? &ka.mig_tab[PK_GEOM(w.packed[td[0]])].cand[sel] : nullptr;
+    if (pc == nullptr || pc->mem < 0) { REASON(14 /*ModeNotFit*/); return false; }
+    const int pmem = pc->mem, pcore = (int)pc->core, slices = hs_enf_i32(*pc, 0);
+    uint32_t useMaskE = 0xffu, nouseMaskE = 0u;
+    if (e.has_use) useMaskE = uuid_mask_lookup(ka.uuid_pool, e.use_off, e.use_cnt, node);
+    if (e.nouse_cnt) nouseMaskE = uuid_mask_lookup(ka.uuid_pool, e.nouse_off, e.nouse_cnt, node);
+    for (int i = cnt - 1; i >= 0; i--) {
+      const int d = td[i];
+      if (!(w.dflags[d] & DF_HEALTH)) { REASON(6); continue; }
+      if (!((e.type_allow >> PK_TYPE(w.packed[d])) & 1ull)) { REASON(0); continue; }
+      if (!((useMaskE >> d) & 1u) || ((nouseMaskE >> d) & 1u)) { REASON(1); continue; }
+      if (w.count[d] <= w.used[d]) { REASON(2); continue; }
+      if (isMutex && w.used[d] > 0) { REASON(9); continue; }
+      if (w.totmem[d] - w.mem[d] < pmem) { REASON(4); continue; }
+      if (w.totcore[d] > 0 && w.totcore[d] - w.cores[d] < pcore) { REASON(5); continue; }
+      if (k_nums > 0) {
+        k_nums--;
+        fc.tmp_dev[fc.ntmp] = d;
+        fc.tmp_mem[fc.ntmp] = pmem;
+        fc.tmp_cores[fc.ntmp] = pcore;
+        fc.tmp_aws[fc.ntmp] = sel | (slices << 8);       // the profile and its slice count ride along to AddResourceUsage
+        fc.ntmp++;
+      }
+      if (k_nums == 0) return true;
+    }
+    if (MODE == EV_EXPLAIN && fc.ntmp > 0) out.reasons[12] = (uint32_t)fc.ntmp;
+    return false;
+  }
   if (e.flags & EF_KUNLUN) {
     // kunlun whole XPUs: graghSelect (kunlun/topo.go:206-252) over the typeDevices in LIST order; fitFn = both uuid pairs
     // (merged into one use / no-use list on the host) and FitXPU = idle and healthy (device.go:196-206,238-240)
@@ -701,7 +733,16 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
         if (w.aws[d] < 0) w.aws[d] = 0;
         w.aws[d] += fc.tmp_aws[t];
       }
-      if (e.flags & EF_VXPU) {
+      if (e.flags & EF_ENFLAME) {         // enflame/device.go:372-380: Used grows by the profile's slice count
+        pick_cores = fc.tmp_cores[t];
+        mig_sel = fc.tmp_aws[t] & 15;     // reported like a MIG pick: the candidate index in the row's spare bits
+        int s = fc.tmp_aws[t] >> 8;
+        s = s <= 0 ? 1 : s;
+        const long long u = (long long)w.used[d] + s;
+        w.used[d] = u > 2147483647LL ? 2147483647 : (int)u;
+        w.cores[d] += pick_cores;
+        w.mem[d] += fc.tmp_mem[t];
+      } else if (e.flags & EF_VXPU) {
         pick_cores = fc.tmp_cores[t];     // the request's Coresreq as asked (vdevice.go:283)
         w.used[d] += 1;
         w.cores[d] += pick_cores;

@@ -401,6 +401,130 @@ bool decode_node_json(const std::string& s, std::vector<Device>& out, std::strin
 // false on ANY error, as the caller there turns every error into 0: a syntax error, a document that is not an object
 // (null is fine and leaves the map empty), a key strconv.ParseInt rejects, a value that is not an integer number
 // (null is fine and stores 0).  A later duplicate key wins.
+// enflame GetNodeDevices, enflame/device.go:198-252 (parseProfile :621-643, parseDRSCapacity :659-683)
+static void enf_profile_parts(const std::string& name, int64_t& size, int64_t& mem_gb) {
+  size = 0; mem_gb = 0;
+  std::string n;
+  {   // strings.ToLower(strings.TrimSpace(name))
+    size_t a = 0, b = name.size();
+    while (a < b && (name[a] == ' ' || (name[a] >= '\t' && name[a] <= '\r'))) a++;
+    while (b > a && (name[b - 1] == ' ' || (name[b - 1] >= '\t' && name[b - 1] <= '\r'))) b--;
+    n = name.substr(a, b - a);
+    for (auto& c : n) if (c >= 'A' && c <= 'Z') c = (char)(c + 32);
+  }
+  const size_t dot = n.find('.');
+  if (dot == std::string::npos) return;
+  const size_t dot2 = n.find('.', dot + 1);
+  auto trim = [](std::string t) {
+    size_t a = 0, b = t.size();
+    while (a < b && (t[a] == ' ' || (t[a] >= '\t' && t[a] <= '\r'))) a++;
+    while (b > a && (t[b - 1] == ' ' || (t[b - 1] >= '\t' && t[b - 1] <= '\r'))) b--;
+    return t.substr(a, b - a);
+  };
+  std::string sp = trim(n.substr(0, dot));
+  if (!sp.empty() && sp.back() == 'g') sp.pop_back();
+  std::string e;
+  int64_t v;
+  if (!parse_int(sp, 64, "Atoi", v, e)) return;
+  size = v;
+  std::string mp = trim(dot2 == std::string::npos ? n.substr(dot + 1) : n.substr(dot + 1, dot2 - dot - 1));
+  if (mp.size() >= 2 && mp.compare(mp.size() - 2, 2, "gb") == 0) mp.erase(mp.size() - 2);
+  if (!parse_int(mp, 64, "Atoi", v, e)) return;
+  mem_gb = v;
+}
+bool enflame_devices_from_drs(const std::string& json, const std::string& node, std::vector<Device>& out, std::string& err) {
+  out.clear();
+  JParser p(json);
+  JV doc;
+  if (!p.document(doc)) { err = "failed to parse enflame.com/gcu-drs-capacity: " + p.err; return false; }
+  std::vector<std::pair<std::string, std::string>> profiles;
+  const JV* devs = nullptr;
+  if (doc.kind == JV::Obj)
+    for (const auto& kv : doc.o) {
+      if (key_is(kv.first, "devices")) {
+        if (kv.second.kind == JV::Arr) devs = &kv.second;
+        else if (kv.second.kind != JV::Null) { err = "failed to parse enflame.com/gcu-drs-capacity: json: cannot unmarshal " + std::string(kind_name(kv.second)) + " into Go struct field drsCapacitySpec.devices of type []enflame.drsDeviceSpec"; return false; }
+        else devs = nullptr;
+      } else if (key_is(kv.first, "profiles")) {
+        profiles.clear();
+        if (kv.second.kind == JV::Obj) {
+          for (const auto& pr : kv.second.o) {
+            if (pr.second.kind != JV::Str && pr.second.kind != JV::Null) { err = "failed to parse enflame.com/gcu-drs-capacity: json: cannot unmarshal " + std::string(kind_name(pr.second)) + " into Go struct field drsCapacitySpec.profiles of type string"; return false; }
+            bool found = false;
+            for (auto& q : profiles) if (q.first == pr.first) { q.second = pr.second.s; found = true; }
+            if (!found) profiles.emplace_back(pr.first, pr.second.kind == JV::Str ? pr.second.s : std::string());
+          }
+        } else if (kv.second.kind != JV::Null) { err = "failed to parse enflame.com/gcu-drs-capacity: json: cannot unmarshal " + std::string(kind_name(kv.second)) + " into Go struct field drsCapacitySpec.profiles of type map[string]string"; return false; }
+      }
+    }
+  else if (doc.kind != JV::Null) { err = "failed to parse enflame.com/gcu-drs-capacity: json: cannot unmarshal " + std::string(kind_name(doc)) + " into Go value of type enflame.drsCapacitySpec"; return false; }
+  int64_t maxSlice = 0, maxMemGB = 0;
+  for (const auto& pr : profiles) {
+    int64_t s, m;
+    enf_profile_parts(pr.first, s, m);
+    if (s > maxSlice) maxSlice = s;
+    if (m > maxMemGB) maxMemGB = m;
+  }
+  if (maxSlice <= 0) { err = "no valid drs profiles found on node " + node; return false; }
+  if (maxMemGB <= 0) maxMemGB = maxSlice;
+  if (maxSlice > 2147483647LL) { err = "drs profile slice count outside int32"; return false; }
+  size_t idx = 0;
+  if (devs)
+    for (const JV& d : devs->a) {
+      std::string index, minor;
+      const JV* cap = nullptr;
+      if (d.kind == JV::Obj)
+        for (const auto& f : d.o) {
+          if (key_is(f.first, "index")) { if (f.second.kind == JV::Str) index = f.second.s; else if (f.second.kind != JV::Null) { err = "failed to parse enflame.com/gcu-drs-capacity: json: cannot unmarshal " + std::string(kind_name(f.second)) + " into Go struct field drsDeviceSpec.devices.index of type string"; return false; } }
+          else if (key_is(f.first, "minor")) { if (f.second.kind == JV::Str) minor = f.second.s; else if (f.second.kind != JV::Null) { err = "failed to parse enflame.com/gcu-drs-capacity: json: cannot unmarshal " + std::string(kind_name(f.second)) + " into Go struct field drsDeviceSpec.devices.minor of type string"; return false; } }
+          else if (key_is(f.first, "capacity")) cap = &f.second;
+        }
+      else if (d.kind != JV::Null) { err = "failed to parse enflame.com/gcu-drs-capacity: json: cannot unmarshal " + std::string(kind_name(d)) + " into Go value of type enflame.drsDeviceSpec"; return false; }
+      int64_t devIndex = (int64_t)idx;
+      {
+        std::string e; int64_t v;
+        if (parse_int(index, 64, "Atoi", v, e)) devIndex = v;
+      }
+      int64_t capacity = 0;
+      bool cap_ok = false;
+      if (cap && cap->kind == JV::Num) {                      // float64: int32(typed) after the range check
+        char* endp = nullptr;
+        const double x = strtod(cap->s.c_str(), &endp);
+        if (x == x && x <= 2147483647.0 && x >= -2147483648.0) { capacity = (int64_t)x; cap_ok = true; }
+      } else if (cap && cap->kind == JV::Str) {
+        std::string t = cap->s, e;
+        size_t a = 0, b = t.size();
+        while (a < b && (t[a] == ' ' || (t[a] >= '\t' && t[a] <= '\r'))) a++;
+        while (b > a && (t[b - 1] == ' ' || (t[b - 1] >= '\t' && t[b - 1] <= '\r'))) b--;
+        int64_t v;
+        if (parse_int(t.substr(a, b - a), 64, "Atoi", v, e)) { capacity = v > 2147483647LL ? 2147483647LL : (v < -2147483648LL ? -2147483648LL : v); cap_ok = true; }
+      }
+      if (!cap_ok || capacity <= 0) { err = "invalid drs capacity on node " + node; out.clear(); return false; }
+      if (devIndex < 0 || devIndex > 255) { err = "drs device index does not fit the engine's 8-bit device index"; out.clear(); return false; }
+      Device dv;
+      dv.index = (uint32_t)devIndex;
+      dv.id = node + "-enflame-drs-" + std::to_string(devIndex);
+      dv.count = (int32_t)capacity;
+      dv.devmem = (int32_t)(uint32_t)((uint64_t)maxMemGB * 1024u);      // int32(maxMemGB * 1024)
+      dv.devcore = 100; dv.type = "Enflame"; dv.numa = 0; dv.health = true;
+      dv.has_enflame = true;
+      {
+        size_t a = 0, b = minor.size();
+        while (a < b && (minor[a] == ' ' || (minor[a] >= '\t' && minor[a] <= '\r'))) a++;
+        while (b > a && (minor[b - 1] == ' ' || (minor[b - 1] >= '\t' && minor[b - 1] <= '\r'))) b--;
+        dv.enf_minor = minor.substr(a, b - a);
+      }
+      if (dv.enf_minor.empty()) dv.enf_minor = std::to_string(devIndex);
+      dv.enf_index = std::to_string(devIndex);
+      dv.enf_profiles = profiles;
+      dv.enf_max_slice = (int32_t)maxSlice;
+      out.push_back(dv);
+      idx++;
+    }
+  if (out.empty()) { err = "no drs devices found on node " + node; return false; }
+  return true;
+}
+
 // nvidia.DecodeMigAllocations, nvidia/mig_allocations.go:78-112
 bool decode_mig_allocations(const std::string& json, std::vector<MigReservationRec>& out, std::string& err) {
   out.clear();

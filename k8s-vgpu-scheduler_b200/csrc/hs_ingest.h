@@ -25,6 +25,11 @@ struct Device {            // device.DeviceInfo, the fields the scheduler path r
   bool has_mig_profiles = false;
   std::vector<MigProfileRec> mig_profiles;   // DeviceInfo.MIGProfiles
   bool die_strategy = false; // CustomInfo["DeviceStrategy"] == "die" (vastai die mode)
+  // enflame DRS CustomInfo (enflame/device.go:235-252)
+  bool has_enflame = false;
+  std::string enf_minor, enf_index;
+  std::vector<std::pair<std::string, std::string>> enf_profiles;
+  int32_t enf_max_slice = 0;
   bool has_aic = false;      // CustomInfo["AIC"] is a string: the card the die sits on (vastai/device.go:374-387)
   std::string aic;
 };
@@ -49,6 +54,8 @@ bool neuron_devices_from_capacity(const std::string& node, int64_t counts, int64
 // to no reservation; false + err on malformed JSON, an incomplete entry, a partial runtime identity or a duplicate
 // (containerIndex, deviceIndex) — the caller then treats the pod as carrying no reservation (scheduler.go:760-766)
 bool decode_mig_allocations(const std::string& json, std::vector<MigReservationRec>& out, std::string& err);
+// enflame GetNodeDevices (enflame/device.go:198-252): the node's enflame.com/gcu-drs-capacity annotation
+bool enflame_devices_from_drs(const std::string& json, const std::string& node, std::vector<Device>& out, std::string& err);
 // json.Unmarshal into map[int]int as parseMetaxAnnos uses it (metax/device.go:168-183): false on any error
 bool decode_int_map(const std::string& json, std::vector<std::pair<int64_t, int64_t>>& out);
 // scores[i*n+j] = Scores[devs[j].id] of the pair-score record whose uuid is devs[i].id (0 where absent)

@@ -62,7 +62,7 @@ __device__ void collapse_rows(const DevEntry* ent, const DevAlloc* al, uint32_t 
       if (ent[AL_ENTRY(al[j])].key_id == key && AL_DEV(al[j]) == dev) { first = false; break; }
     if (!first) continue;
     // a pick on a GPU in MIG mode: the cached pod carries no reservation yet, so the GPU fails closed (.w bit 0)
-    if (AL_MIG(al[i])) delta[dev].w = 1;
+    if (AL_MIG(al[i]) && ent[AL_ENTRY(al[i])].vendor == HV_NVIDIA) delta[dev].w = 1;      // (enflame picks use the same spare bits for their profile)
     int imem = 0, icores = 0, islots = 0, amem = 0, acores = 0, aslots = 0;
     for (uint32_t j = i; j < n; j++) {
       if (ent[AL_ENTRY(al[j])].key_id != key || AL_DEV(al[j]) != dev) continue;

@@ -32,6 +32,26 @@ const hs_quantity* lookup_limits(const hs_container_resources* c, const char* na
 
 // returns false for the zero-value ContainerDeviceRequest{}
 bool generate(const hs_vendor_resources& v, const hs_container_resources* c, hs_container_request& r) {
+  if (v.kind == HS_REQ_ENFLAME) {
+    // enflame/device.go:322-366: a positive enflame.com/drs-gcu count is a DIRECT slice request; otherwise memory / core by
+    // spec (getContainerResourceRequest :747-758: Quantity.Value() of Limits, then Requests)
+    r.key = v.common_word; r.type = v.common_word; r.nums = 1;
+    const hs_quantity* q = lookup(c, v.count_name);
+    if (q && q->as_int64_ok && q->as_int64 > 0) {
+      if (q->as_int64 > kMaxInt32) return false;
+      r.memreq = (int32_t)q->as_int64; r.mempct = 0; r.coresreq = 0;
+      return true;
+    }
+    const hs_quantity* mem = lookup(c, v.memory_name);
+    const hs_quantity* core = lookup(c, v.cores_name);
+    if (!mem && !core) return false;
+    if (mem && mem->value > kMaxInt32) return false;
+    if (core && core->value > kMaxInt32) return false;
+    r.memreq = mem ? (int32_t)mem->value : 0;
+    r.coresreq = core ? (int32_t)core->value : 0;
+    r.mempct = -1;
+    return true;
+  }
   if (v.kind == HS_REQ_NEURON) {
     // awsneuron/device.go:287-334: by device (count_name) or, when that is absent, by NeuronCore (cores_name) through
     // splitCoreRequest (:141-154); validateResourceRequest (:115-129): an integer in (0, max]; default_cores carries the
@@ -180,6 +200,8 @@ bool generate(const hs_vendor_resources& v, const hs_container_resources* c, hs_
       corenum = corenum / (int32_t)n;
       break;
     }
+    case HS_REQ_ENFLAME:                                      // handled before the count lookup (two request shapes)
+      return false;
     case HS_REQ_KUNLUN_VXPU: {                                // kunlun/vdevice.go:173-213: memory rounded up to 24576 / 49152 / 98304
       if (mem && mem->as_int64_ok) memnum = mem->as_int64 <= 24576 ? 24576 : (mem->as_int64 <= 49152 ? 49152 : 98304);   // trimMemory, :62-70
       corenum = (int32_t)(memnum * 100 / 98304);

@@ -70,6 +70,7 @@ enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
 #define EF_VASTAI 512u     // vastai: EF_COUNT_ONLY gates; on a node of dies (NetworkID = AIC) card exclusivity under mutex, pick by card, ScoreNode
 #define EF_KUNLUN 1024u    // kunlun whole XPUs (kunlun/device.go:184-240, topo.go): graghSelect over list positions, slot-only usage, ScoreNode by wings
 #define EF_VXPU 2048u      // with EF_KUNLUN: the shared "XPU" type (kunlun/vdevice.go:231-306): FitVXPU, full usage, no ScoreNode
+#define EF_ENFLAME 4096u   // enflame shared vGCU (enflame/device.go:382-478): one DRS profile per request from the node's table, then the gates
 #define EF_COUNT_ONLY 8u   // biren's Fit (biren/device.go:190-248): gates end after mutex; the pick has Usedmem 0, Usedcores = Coresreq
 
 struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 64 B
@@ -169,6 +170,31 @@ HS_HD inline int hs_mig_select(const MigGeom& g, uint32_t occupied, int memory) 
       const uint32_t m = hs_mig_mask(g.cand[c].place[p]);
       if (!(m & occupied)) return (int)c | (p << 4) | (int)(m << 8);
     }
+  }
+  return -1;
+}
+
+// enflame's DRS profiles of a node ride in the same table (PK_GEOM of its devices): one MigCand per candidate in
+// selectProfileByRequest's order, mem = the profile's MiB (-1: a profile the reference rejects as ModeNotFit), core = its
+// core share, place[0..3] = slice count, place[4..7] = GB (both int32, little endian).
+HS_HD inline int hs_enf_i32(const MigCand& c, int at) {
+  return (int)((uint32_t)c.place[at] | ((uint32_t)c.place[at + 1] << 8) | ((uint32_t)c.place[at + 2] << 16) | ((uint32_t)c.place[at + 3] << 24));
+}
+// selectProfileByRequest (enflame/device.go:498-531): candidate index or -1
+HS_HD inline int hs_enf_select(const MigGeom& g, int memreq, int mempct, int coresreq) {
+  const int n = (int)(g.n_cand < 16u ? g.n_cand : 16u);
+  if (n == 0) return -1;
+  if (mempct == 0) {                                   // direct: the slice count itself
+    for (int c = 0; c < n; c++) if (hs_enf_i32(g.cand[c], 0) == memreq) return c;
+    return -1;
+  }
+  const long long maxMemGB = hs_enf_i32(g.cand[n - 1], 4);
+  long long req = 0;                                   // normalizeMemoryRequestToGB, :645-657
+  if (memreq > 0) req = (maxMemGB > 0 && (long long)memreq > maxMemGB * 2) ? ((long long)memreq + 1023) / 1024 : memreq;
+  for (int c = 0; c < n; c++) {
+    if (req > 0 && (long long)hs_enf_i32(g.cand[c], 4) < req) continue;
+    if (coresreq > 0 && (int)g.cand[c].core < coresreq) continue;
+    return c;
   }
   return -1;
 }

@@ -117,6 +117,11 @@ def decode_node_devices(vendor, fmt, annotation, pair_scores=None, node_name=Non
             "Devcore": devs[i].devcore, "Type": devs[i].type.decode(), "Numa": devs[i].numa, "Mode": devs[i].mode.decode(),
             "Health": bool(devs[i].health), "DeviceVendor": devs[i].vendor.decode(), "NetworkID": devs[i].network_id}
            for i in range(n.value)]
+    for i in range(n.value):      # enflame DRS CustomInfo
+        if devs[i].enflame:
+            ef = devs[i].enflame.contents
+            out[i]["Enflame"] = {"minor": ef.minor.decode(), "index": ef.index.decode(), "max_slice": ef.max_slice,
+                                 "profiles": {ef.profiles[k].key.decode(): ef.profiles[k].value.decode() for k in range(ef.n_profiles)}}
     for i in range(n.value):      # DeviceInfo.MIGProfiles, present for GPUs that report any
         if devs[i].n_mig_profiles:
             out[i]["MigProfiles"] = [

@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cassert>
 #include <cstdio>
+#include <cmath>
 #include <cstring>
 #include <functional>
 #include <set>
@@ -1187,6 +1188,116 @@ FitResult fitKunlun(const std::string& word, const std::vector<DeviceUsage*>& de
   return r;
 }
 
+// ---- enflame shared vGCU ("Enflame", enflame/device.go:382-478): one DRS profile per request, chosen from the profiles
+// the node's devices advertise, then the template gates with the profile's memory and core share --------------------
+struct DrsProfile { std::string Name, ID; long long Size = 0, MemoryGB = 0, CorePercent = 0; int RequestMemoryGB = 0, RequestCorePercent = 0; };
+static void parseDrsProfile(const std::string& profileName, long long& size, long long& memGB) {     // parseProfile, :621-643 (Go int is 64 bit)
+  size = 0; memGB = 0;
+  std::string normalized = ToLower(TrimSpace(profileName));
+  std::vector<std::string> parts = Split(normalized, '.');
+  if (parts.size() < 2) return;
+  std::string sizePart = TrimSpace(parts[0]);
+  if (sizePart.size() >= 1 && sizePart.back() == 'g') sizePart.pop_back();
+  long long sz = 0;
+  if (!ParseInt64(sizePart, sz)) return;                         // strconv.Atoi
+  std::string memPart = TrimSpace(parts[1]);
+  if (memPart.size() >= 2 && memPart.compare(memPart.size() - 2, 2, "gb") == 0) memPart.erase(memPart.size() - 2);
+  long long mg = 0;
+  size = sz;
+  if (!ParseInt64(memPart, mg)) return;
+  memGB = mg;
+}
+// collectDRSProfiles, :567-619.  Candidates with equal (Size, MemoryGB) come out of a Go map in random order and an
+// unstable sort: taken in ascending profile name (canonical rule, like the other map-order cases).
+static std::vector<DrsProfile> collectDrsProfiles(const std::vector<DeviceUsage*>& devices) {
+  long long maxSlice = 0;
+  for (auto d : devices) if (d->EnfMaxSlice > maxSlice) maxSlice = d->EnfMaxSlice;
+  if (maxSlice <= 0)
+    for (auto d : devices)
+      for (auto& kv : d->EnfProfiles) { long long size, mem; parseDrsProfile(kv.first, size, mem); if (size > maxSlice) maxSlice = size; }
+  if (maxSlice <= 0) return {};
+  std::map<std::string, DrsProfile> seen;
+  for (auto d : devices)
+    for (auto& kv : d->EnfProfiles) {
+      long long size, memGB;
+      parseDrsProfile(kv.first, size, memGB);
+      if (size <= 0 || memGB <= 0) continue;
+      DrsProfile c;
+      c.Name = kv.first; c.ID = kv.second; c.Size = size; c.MemoryGB = memGB;
+      c.CorePercent = (long long)std::ceil((double)size * 100 / (double)maxSlice);
+      seen[kv.first] = c;
+    }
+  std::vector<DrsProfile> candidates;
+  for (auto& kv : seen) candidates.push_back(kv.second);          // ascending name
+  std::stable_sort(candidates.begin(), candidates.end(), [](const DrsProfile& a, const DrsProfile& b) {
+    if (a.Size == b.Size) return a.MemoryGB < b.MemoryGB;
+    return a.Size < b.Size;
+  });
+  return candidates;
+}
+static bool selectDrsProfile(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, DrsProfile& out) {   // :498-531
+  std::vector<DrsProfile> candidates = collectDrsProfiles(devices);
+  if (candidates.empty()) return false;
+  if (request.MemPercentagereq == 0) {                              // enflameRequestModeDirect: the slice count itself
+    for (auto& c : candidates) if (c.Size == (long long)request.Memreq) { out = c; return true; }
+    return false;
+  }
+  const long long maxMemGB = candidates.back().MemoryGB;
+  int requestMemGB;                                                 // normalizeMemoryRequestToGB, :645-657
+  if (request.Memreq <= 0) requestMemGB = 0;
+  else if (maxMemGB <= 0) requestMemGB = (int)request.Memreq;
+  else if ((long long)request.Memreq > (long long)maxMemGB * 2) requestMemGB = (int)std::ceil((double)request.Memreq / 1024.0);
+  else requestMemGB = (int)request.Memreq;
+  const int requestCorePercent = (int)request.Coresreq;
+  for (auto& c : candidates) {
+    if (requestMemGB > 0 && c.MemoryGB < requestMemGB) continue;
+    if (requestCorePercent > 0 && c.CorePercent < requestCorePercent) continue;
+    out = c;
+    out.RequestMemoryGB = requestMemGB; out.RequestCorePercent = requestCorePercent;
+    return true;
+  }
+  return false;
+}
+FitResult fitEnflame(const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
+                     const std::string& gpuPolicyDefault) {
+  ContainerDeviceRequest k = request;
+  const int32_t originReq = k.Nums;
+  std::map<std::string, int> reason;
+  const bool isMutex = PolicyContains(GetGPUSchedulerPolicyByPod(gpuPolicyDefault, pod), "mutex");
+  FitResult r;
+  DrsProfile profile;
+  auto modeNotFit = [&]() { reason["ModeNotFit"]++; r.fit = false; r.reason = GenReason(reason, (int)devices.size()); return r; };
+  if (!selectDrsProfile(devices, k, profile)) return modeNotFit();
+  if (profile.Size <= 0 || profile.Size > 2147483647LL) return modeNotFit();
+  if (profile.MemoryGB <= 0 || profile.MemoryGB > 2147483647LL / 1024) return modeNotFit();
+  if (profile.CorePercent > 2147483647LL) return modeNotFit();
+  const int32_t profileMemoryMiB = (int32_t)(profile.MemoryGB * 1024);
+  const int32_t profileCorePercent = (int32_t)profile.CorePercent;
+  for (int i = (int)devices.size() - 1; i >= 0; i--) {
+    DeviceUsage* dev = devices[i];
+    if (!dev->Health) { reason["CardNotHealth"]++; continue; }
+    if (k.Type != "Enflame") { reason["CardTypeMismatch"]++; continue; }                       // checkType, :310-315
+    if (!CheckUUID(pod.Annotations, dev->ID, "enflame.com/use-gpuuuid", "enflame.com/nouse-gpuuuid")) { reason["CardUuidMismatch"]++; continue; }
+    if (dev->Count <= dev->Used) { reason["CardTimeSlicingExhausted"]++; continue; }
+    if (isMutex && dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+    if (i32sub(dev->Totalmem, dev->Usedmem) < profileMemoryMiB) { reason["CardInsufficientMemory"]++; continue; }
+    if (dev->Totalcore > 0 && i32sub(dev->Totalcore, dev->Usedcores) < profileCorePercent) { reason["CardInsufficientCore"]++; continue; }
+    if (k.Nums > 0) {
+      k.Nums--;
+      ContainerDevice cd;
+      cd.Idx = (int)dev->Index; cd.UUID = dev->ID; cd.Type = k.Type; cd.Usedmem = profileMemoryMiB; cd.Usedcores = profileCorePercent;
+      cd.HasDrs = true; cd.DrsProfileName = profile.Name; cd.DrsProfileID = profile.ID; cd.DrsMinor = dev->EnfMinor; cd.DrsIndex = dev->EnfIndex;
+      cd.DrsSlice = (int)profile.Size; cd.DrsRequestMem = profile.RequestMemoryGB; cd.DrsRequestCore = profile.RequestCorePercent;
+      r.devs.push_back(cd);
+    }
+    if (k.Nums == 0) { r.fit = true; return r; }
+  }
+  if (!r.devs.empty()) reason["AllocatedCardsInsufficientRequest"] = (int)r.devs.size();
+  r.fit = false; r.reason = GenReason(reason, (int)devices.size());
+  (void)originReq;
+  return r;
+}
+
 // iluvatar (one instance per CommonWord, iluvatar/device.go:60-83) and biren (biren/device.go:54-66)
 class PlainDevices : public Devices {
  public:
@@ -1197,6 +1308,7 @@ class PlainDevices : public Devices {
                 const QuotaManager* quota) const override {
     static const Vendor kinds[] = {Vendor::PLAIN, Vendor::COUNT_ONLY, Vendor::AMD, Vendor::MTHREADS, Vendor::WHOLE_CARD, Vendor::METAX,
                                    Vendor::PLAIN /* 6 = Neuron, below */, Vendor::VASTAI};
+    if (v_.FitKind == 10) return fitEnflame(devices, request, pod, def);
     if (v_.FitKind == 8 || v_.FitKind == 9) return fitKunlun(v_.CommonWord, devices, request, pod, v_.FitKind == 9, def);
     FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 7 ? v_.FitKind : 0],
                v_.CommonWord,
@@ -1206,6 +1318,14 @@ class PlainDevices : public Devices {
   }
   bool AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const override {
     if (v_.FitKind == 8) { n.Used = i32add(n.Used, 1); return true; }      // kunlun/device.go:179-182: the slot only
+    if (v_.FitKind == 10) {                                                // enflame/device.go:372-380: the slot count grows by the slice size
+      int slice = ctr.DrsSlice <= 0 ? 1 : ctr.DrsSlice;
+      long long u = (long long)n.Used + slice;
+      n.Used = (int32_t)std::min<long long>(std::max<long long>(u, -2147483648LL), 2147483647LL);      // clampToInt32
+      n.Usedcores = i32add(n.Usedcores, ctr.Usedcores);
+      n.Usedmem = i32add(n.Usedmem, ctr.Usedmem);
+      return true;
+    }
     Devices::AddResourceUsage(n, ctr);
     if (v_.FitKind == 6) {                       // awsneuron/device.go:340-355
       if (n.AwsUsage < 0) n.AwsUsage = 0;
@@ -1258,7 +1378,7 @@ class PlainDevices : public Devices {
     }
     return res;
   }
-  void PatchAnnotations(const Pod&, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
+  void PatchAnnotations(const Pod& pod, std::map<std::string, std::string>& annos, const PodDevices& pd) const override {
     // iluvatar/device.go:143-154, biren/device.go:167-177, metax/device.go:91-103
     auto it = pd.find(v_.CommonWord);
     if (it != pd.end() && !it->second.empty()) {
@@ -1281,6 +1401,37 @@ class PlainDevices : public Devices {
           annos["mthreads.com/gpu-index"] = value;
           annos["mthreads.com/predicate-time"] = "";
           annos["mthreads.com/predicate-node"] = annos["hami.io/vgpu-node"];
+        }
+        return;
+      }
+      if (v_.FitKind == 10) {
+        // enflame/device.go:254-300: the allocated key, gcu-assigned = "false", a timestamp (blanked, canonical rule 6), the
+        // first container's index / minor / slice count, and assigned-containers = {container name: request} as JSON
+        annos[v_.Allocated] = s;
+        annos["enflame.com/gcu-assigned"] = "false";
+        annos["enflame.com/gcu-assigned-time"] = "";
+        std::map<std::string, std::string> assigned;
+        for (size_t ctridx = 0; ctridx < it->second.size(); ctridx++) {
+          const ContainerDevices& ctrDevices = it->second[ctridx];
+          if (ctrDevices.empty()) continue;
+          const ContainerDevice& chosen = ctrDevices[0];
+          int slice = chosen.DrsSlice <= 0 ? 1 : chosen.DrsSlice;
+          std::string ctrName = ctridx < pod.ContainerNames.size() ? pod.ContainerNames[ctridx] : "container-" + std::to_string(ctridx);
+          std::string o = "{\"allocated\":false,\"request\":" + std::to_string(slice);
+          if (!chosen.DrsProfileID.empty()) o += ",\"profileID\":" + jsonString(chosen.DrsProfileID);
+          if (!chosen.DrsProfileName.empty()) o += ",\"profileName\":" + jsonString(chosen.DrsProfileName);
+          assigned[ctrName] = o + "}";
+          if (!annos.count("enflame.com/gcu-assigned-index") && !chosen.DrsIndex.empty()) {
+            annos["enflame.com/gcu-assigned-index"] = chosen.DrsIndex;
+            annos["enflame.com/gcu-assigned-id"] = chosen.DrsIndex;
+          }
+          if (!annos.count("enflame.com/gcu-assigned-minor") && !chosen.DrsMinor.empty()) annos["enflame.com/gcu-assigned-minor"] = chosen.DrsMinor;
+          if (!annos.count("enflame.com/gcu-request-size") && slice > 0) annos["enflame.com/gcu-request-size"] = std::to_string(slice);
+        }
+        if (!assigned.empty()) {
+          std::string payload = "{";
+          for (auto& kv : assigned) { if (payload.size() > 1) payload += ","; payload += jsonString(kv.first) + ":" + kv.second; }
+          annos["assigned-containers"] = payload + "}";
         }
         return;
       }
@@ -1478,6 +1629,7 @@ void Scheduler::AddNode(const NodeInfo& info) {
       u.Mode = d.Mode; u.Type = d.Type; u.Numa = d.Numa; u.Health = d.Health;
       u.HasNetworkID = d.HasNetworkID; u.NetworkID = d.NetworkID;
       u.MigProfiles = d.MIGProfiles;   // scheduler.go:678
+      u.EnfMinor = d.EnfMinor; u.EnfIndex = d.EnfIndex; u.EnfProfiles = d.EnfProfiles; u.EnfMaxSlice = d.EnfMaxSlice;   // CustomInfo, :684
       usage.push_back(u);
     }
   }

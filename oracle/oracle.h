@@ -81,6 +81,10 @@ struct DeviceUsage {               // devices.go:106-125
   int AwsUsage = -1;               // CustomInfo["awsusageinfo"] (awsneuron/device.go:340-355,485-488), -1 = key absent
   std::vector<MigProfile> MigProfiles;            // devices.go:116
   std::vector<MigAllocation> MigAllocationsInUse; // devices.go:117
+  // enflame shared vGCU: CustomInfo["minor"], ["index"], ["profiles"] (name -> id), ["maxSlice"] (enflame/device.go:235-252)
+  std::string EnfMinor, EnfIndex;
+  std::vector<std::pair<std::string, std::string>> EnfProfiles;
+  int EnfMaxSlice = 0;
 };
 
 struct DeviceInfo {                // devices.go:127-144
@@ -96,6 +100,9 @@ struct DeviceInfo {                // devices.go:127-144
   int NetworkID = 0;
   std::map<std::string, int> PairScores;  // DevicePairScore.Scores
   std::vector<MigProfile> MIGProfiles;    // devices.go:141
+  std::string EnfMinor, EnfIndex;         // CustomInfo of an enflame DRS device
+  std::vector<std::pair<std::string, std::string>> EnfProfiles;
+  int EnfMaxSlice = 0;
 };
 
 struct NodeInfo {                  // devices.go:170-174 (+ the node annotations Fit reads)
@@ -116,6 +123,10 @@ struct ContainerDevice {           // devices.go:205-216
   bool HasMig = false;             // CustomInfo["migProfile"] / ["migPlacement"] set by the NVIDIA AddResourceUsage (nvidia/device.go:653-657)
   std::string MigProfileName;
   MigPlacement MigPlace;
+  // enflame Fit's CustomInfo (enflame/device.go:452-460): profileName / profileID / minor / index / drsSlice
+  bool HasDrs = false;
+  std::string DrsProfileName, DrsProfileID, DrsMinor, DrsIndex;
+  int DrsSlice = 0, DrsRequestMem = 0, DrsRequestCore = 0;
 };
 
 struct ContainerDeviceRequest {    // devices.go:222-228
@@ -134,6 +145,7 @@ struct Pod {                       // the parts of corev1.Pod the path reads
   std::string UID, Namespace, Name;
   std::map<std::string, std::string> Annotations;
   int NumInitContainers = 0;
+  std::vector<std::string> ContainerNames;   // init containers first; "" = unnamed (enflame's assigned-containers annotation is keyed by them)
   PodDeviceRequests Reqs;          // device.Resourcereqs(pod), devices.go:639-691
 };
 

@@ -51,6 +51,7 @@ Pod toPod(const hs_pod* p) {
       m[str(q.key)] = k;
     }
     pod.Reqs.push_back(m);
+    pod.ContainerNames.push_back(p->containers[c].name ? str(p->containers[c].name) : "container-" + std::to_string(c));   // containerNameByIndex, enflame/device.go:692-705
   }
   return pod;
 }
@@ -78,6 +79,10 @@ NodeInfo toNodeInfo(const hs_node_info* n) {
     di.DeviceVendor = str(d.vendor);
     di.HasNetworkID = d.network_id >= 0; di.NetworkID = d.network_id >= 0 ? d.network_id : 0;
     di.MIGProfiles = toMigProfiles(d.mig_profiles, d.n_mig_profiles);
+    if (d.enflame) {
+      di.EnfMinor = str(d.enflame->minor); di.EnfIndex = str(d.enflame->index); di.EnfMaxSlice = d.enflame->max_slice;
+      for (uint32_t k = 0; k < d.enflame->n_profiles; k++) di.EnfProfiles.emplace_back(str(d.enflame->profiles[k].key), str(d.enflame->profiles[k].value));
+    }
     if (n->pair_scores)
       for (uint32_t j = 0; j < n->n_devices; j++)
         if (j != i) di.PairScores[str(n->devices[j].id)] = n->pair_scores[i * n->n_devices + j];
@@ -98,6 +103,10 @@ DeviceListsScore toDls(const oracle_dev& d) {
   ds.Device.Health = d.health != 0; ds.Device.HasNetworkID = d.network_id >= 0;
   ds.Device.NetworkID = d.network_id >= 0 ? d.network_id : 0;
   ds.Device.MigProfiles = toMigProfiles(d.mig_profiles, d.n_mig_profiles);
+  if (d.enflame) {
+    ds.Device.EnfMinor = str(d.enflame->minor); ds.Device.EnfIndex = str(d.enflame->index); ds.Device.EnfMaxSlice = d.enflame->max_slice;
+    for (uint32_t k = 0; k < d.enflame->n_profiles; k++) ds.Device.EnfProfiles.emplace_back(str(d.enflame->profiles[k].key), str(d.enflame->profiles[k].value));
+  }
   for (uint32_t i = 0; d.mig_in_use && i < d.n_mig_in_use; i++)
     ds.Device.MigAllocationsInUse.push_back(MigAllocation{"", MigPlacement{d.mig_in_use[i].start, d.mig_in_use[i].size}});
   ds.Score = d.score;
@@ -114,7 +123,8 @@ void fillEntries(Arena& a, const PodDevices& pd) {
       }
       for (auto& cd : kv.second[c])
         a.entries.push_back(hs_alloc_entry{(uint32_t)c, key, a.s(cd.UUID), cd.Idx, cd.Usedmem, cd.Usedcores,
-                                           cd.HasMig ? a.s(cd.MigProfileName) : nullptr, cd.MigPlace.Start, cd.MigPlace.Size});
+                                           cd.HasMig ? a.s(cd.MigProfileName) : (cd.HasDrs ? a.s(cd.DrsProfileName) : nullptr),
+                                           cd.HasDrs ? (uint32_t)cd.DrsSlice : cd.MigPlace.Start, cd.HasDrs ? 0u : cd.MigPlace.Size});
     }
   }
 }
@@ -460,7 +470,8 @@ int32_t oracle_fit(oracle_handle* o, const char* vendor_key, const oracle_dev* d
     FitResult fr = v->Fit(ptrs, k, p, node_info ? &ni : nullptr, o->s->config().GPUSchedulerPolicy);
     out->status = fr.fit ? HS_FIT : HS_NOFIT;
     const char* key = a.s(k.Type);
-    for (auto& cd : fr.devs) a.entries.push_back(hs_alloc_entry{0, key, a.s(cd.UUID), cd.Idx, cd.Usedmem, cd.Usedcores, nullptr, 0, 0});
+    for (auto& cd : fr.devs) a.entries.push_back(hs_alloc_entry{0, key, a.s(cd.UUID), cd.Idx, cd.Usedmem, cd.Usedcores,
+                                                               cd.HasDrs ? a.s(cd.DrsProfileName) : nullptr, cd.HasDrs ? (uint32_t)cd.DrsSlice : 0u, 0});
     a.failed.push_back(hs_failed_node{a.s(""), a.s(fr.reason)});
     finish(a, out);
     return fr.fit ? 1 : 0;

@@ -31,6 +31,7 @@ typedef struct oracle_dev {
   uint32_t                n_mig_profiles;
   const hs_mig_placement* mig_in_use;     /* placements of DeviceUsage.MigAllocationsInUse */
   uint32_t                n_mig_in_use;
+  const hs_enflame_info*  enflame;        /* CustomInfo of an enflame DRS device */
 } oracle_dev;
 
 oracle_handle* oracle_create(const hs_config* cfg);

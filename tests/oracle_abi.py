@@ -20,7 +20,8 @@ class oracle_dev(C.Structure):
                 ("mode", C.c_char_p), ("numa", C.c_int32), ("type", C.c_char_p), ("health", C.c_uint8),
                 ("network_id", C.c_int32), ("score", C.c_float),
                 ("mig_profiles", C.POINTER(abi.hs_mig_profile)), ("n_mig_profiles", C.c_uint32),
-                ("mig_in_use", C.POINTER(abi.hs_mig_placement)), ("n_mig_in_use", C.c_uint32)]
+                ("mig_in_use", C.POINTER(abi.hs_mig_placement)), ("n_mig_in_use", C.c_uint32),
+                ("enflame", C.POINTER(abi.hs_enflame_info))]
 
 
 _lib = None
@@ -101,6 +102,14 @@ def placements_array(pl):
     return arr
 
 
+def enflame_from_go(ci):
+    """Go CustomInfo of an enflame DRS device ({"minor","index","profiles": {name: id},"maxSlice"}) -> hs_enflame_info*"""
+    if not isinstance(ci, dict) or "profiles" not in ci:
+        return None
+    return abi.build_enflame_info({"minor": ci.get("minor", ""), "index": ci.get("index", ""),
+                                   "max_slice": int(ci.get("maxSlice", 0)), "profiles": ci.get("profiles") or {}}, _mig_keep)
+
+
 def dev_from_go(d, score=0.0):
     """Go DeviceUsage literal (fixture dict with Go field names) -> oracle_dev"""
     mp, nmp = abi.build_mig_profiles(mig_profiles_from_go(d.get("MigProfiles")), _mig_keep)
@@ -119,7 +128,7 @@ def dev_from_go(d, score=0.0):
                       int(d.get("Usedmem", 0)), int(d.get("Totalmem", 0)), int(d.get("Totalcore", 0)),
                       int(d.get("Usedcores", 0)), abi._b(d.get("Mode", "")), int(d.get("Numa", 0)),
                       abi._b(d.get("Type", "")), 1 if d.get("Health", False) else 0, net, float(score),
-                      mp, nmp, iu, len(inuse))
+                      mp, nmp, iu, len(inuse), enflame_from_go(ci))
 
 
 def devs_array(devs):

@@ -67,6 +67,18 @@ def oracle_generate(v, limits, requests):
         if not name:
             return None
         return limits.get(name, requests.get(name))
+    if v["kind"] == abi.HS_REQ_ENFLAME:          # enflame/device.go:322-366: direct slices, else memory / core by spec (Quantity.Value())
+        wrap = lambda x: ((x + 2 ** 31) % 2 ** 32) - 2 ** 31   # noqa: E731  int32(x)
+        q = get(v["count"])
+        if q is not None and q[1] and q[0] > 0:
+            return {"Nums": 1, "Type": v["word"], "Memreq": q[0], "MemPercentagereq": 0, "Coresreq": 0} if q[0] <= MAXI32 else None
+        mem, core = get(v["mem"]), get(v["cores"])
+        if mem is None and core is None:
+            return None
+        if (mem is not None and mem[2] > MAXI32) or (core is not None and core[2] > MAXI32):
+            return None
+        return {"Nums": 1, "Type": v["word"], "Memreq": wrap(mem[2]) if mem is not None else 0, "MemPercentagereq": -1,
+                "Coresreq": wrap(core[2]) if core is not None else 0}
     if v["kind"] == abi.HS_REQ_NEURON:           # awsneuron/device.go:287-334 (+ :115-154)
         def valid(q, maxv):
             return q[1] and 0 < q[0] <= maxv
@@ -143,6 +155,8 @@ def oracle_generate(v, limits, requests):
         pctn = 100 if memnum == 0 else 0
     elif v["kind"] == abi.HS_REQ_COUNT:          # biren/device.go:141-165, vastai/device.go:143-167
         memnum, pctn, cores = 0, 100, 0
+    elif v["kind"] == abi.HS_REQ_ENFLAME:        # enflame/device.go:322-366
+        pass                                     # handled before the count lookup below
     elif v["kind"] == abi.HS_REQ_KUNLUN_VXPU:    # kunlun/vdevice.go:173-213 (trimMemory :62-70)
         if mem is not None and mem[1]:
             memnum = 24576 if mem[0] <= 24576 else (49152 if mem[0] <= 49152 else 98304)
@@ -254,6 +268,7 @@ AMD = _plain("AMD", abi.HS_REQ_AMD, "amd.com/gpu", "amd.com/gpu-mem", "amd.com/g
 METAX = _plain("Metax-GPU", abi.HS_REQ_METAX, "metax-tech.com/gpu")
 # the golden table keeps the Go identifiers of the two resource names as its map keys (vdevice_test.go:430,444-445)
 XPU = _plain("XPU", abi.HS_REQ_KUNLUN_VXPU, "KunlunResourceVCount", "KunlunResourceVMemory")
+ENFLAME = _plain("Enflame", abi.HS_REQ_ENFLAME, "enflame.com/drs-gcu", "enflame.com/gcu-memory", "enflame.com/gcu-core")
 NEURON = dict(_plain("AWSNeuron", abi.HS_REQ_NEURON, "aws.amazon.com/neuron", None, "aws.amazon.com/neuroncore"), default_cores=2)
 
 TABLES = [("nvidia_generate_requests", NVIDIA, 15), ("hygon_generate_requests", DCU, 5), ("hygon_generate_requests_range", DCU, 2),
@@ -278,6 +293,23 @@ def test_generate_requests_golden(name, vendor, count):
         assert (strip(got[0]) if got else None) == want, ("product", c["name"])
         if got:
             assert got[0]["key"] == vendor["word"]
+
+
+def test_enflame_generate_requests():
+    # enflame/device_test.go:112-158 (TestGenerateResourceRequests, …_ByMemoryCore) + the fall-through rules of device.go:322-366
+    q = lambda n: (n, True, n, 1)   # noqa: E731
+    v = _plain("Enflame", abi.HS_REQ_ENFLAME, "enflame.com/drs-gcu", "enflame.com/gcu-memory", "enflame.com/gcu-core")
+    got = product_generate([v], {"enflame.com/drs-gcu": q(3)}, {})
+    assert strip(got[0]) == {"Nums": 1, "Type": "Enflame", "Memreq": 3, "MemPercentagereq": 0, "Coresreq": 0}
+    got = product_generate([v], {"enflame.com/gcu-memory": q(20480), "enflame.com/gcu-core": q(40)}, {})
+    assert strip(got[0]) == {"Nums": 1, "Type": "Enflame", "Memreq": 20480, "MemPercentagereq": -1, "Coresreq": 40}
+    got = product_generate([v], {}, {"enflame.com/drs-gcu": q(2)})                       # Requests when Limits has none
+    assert strip(got[0])["Memreq"] == 2 and strip(got[0])["MemPercentagereq"] == 0
+    got = product_generate([v], {"enflame.com/drs-gcu": (0, True, 0, 0), "enflame.com/gcu-core": q(30)}, {})   # count 0: by spec
+    assert strip(got[0]) == {"Nums": 1, "Type": "Enflame", "Memreq": 0, "MemPercentagereq": -1, "Coresreq": 30}
+    assert product_generate([v], {"enflame.com/drs-gcu": q(2 ** 31)}, {}) == []          # too large: the zero request
+    assert product_generate([v], {"enflame.com/gcu-memory": q(2 ** 31)}, {}) == []
+    assert product_generate([v], {}, {}) == []
 
 
 def test_nvidia_memory_factor_and_default_memory():
@@ -322,7 +354,7 @@ def test_product_matches_restatement_on_random_containers():
     rng = random.Random(42)
     vendors = [NVIDIA, dict(NVIDIA, word="NV2", factor=4, default_mem=777, default_cores=5), DCU, dict(DCU, word="DCU2", factor=3),
                MLU, ASCEND_910A, ASCEND_CORE, dict(ASCEND_CORE, word="AscF", factor=2),
-               ILUVATAR, BIREN, MTHREADS, GCU, AMD, METAX, XPU, NEURON, dict(NEURON, word="Neuron1", default_cores=1),
+               ILUVATAR, BIREN, MTHREADS, GCU, AMD, METAX, XPU, ENFLAME, NEURON, dict(NEURON, word="Neuron1", default_cores=1),
                dict(NEURON, word="Neuron0", default_cores=0)]
     names = sorted({v[k] for v in vendors for k in ("count", "mem", "pct", "cores") if v[k]})
     pool = [0, 1, 2, 8, -1, -100, 100, 101, 150, 4096, 2 ** 31 - 1, 2 ** 31, 2200000000, 2 ** 32 + 50, 8388607, 8388608,
