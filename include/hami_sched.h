@@ -64,6 +64,9 @@ enum {
   HS_R_AllocatedCardsInsufficientRequest,
   HS_R_ResourceQuotaNotFit,
   HS_R_ModeNotFit,
+  HS_R_CardUnhealthy,             /* metax sGPU's own three (metax/sdevice.go:50-54) */
+  HS_R_CardAppClassMismatch,
+  HS_R_CardQosPolicyMismatch,
   HS_R_COUNT
 };
 
@@ -100,6 +103,13 @@ typedef struct hs_enflame_info {
   uint32_t     n_profiles;
 } hs_enflame_info;
 
+/* CustomInfo of a metax sGPU device (metax/protocol.go:96-116): the QoS policy the device runs ("", "best-effort",
+ * "fixed-share", "burst-share") and its MetaLink zone (0 = none).                                                    */
+typedef struct hs_metax_sgpu_info {
+  const char* qos_policy;
+  int32_t     link_zone;
+} hs_metax_sgpu_info;
+
 /* device.DeviceInfo (pkg/device/devices.go:127-144) as the register path hands
  * it to nodeManager.addNode (pkg/scheduler/nodes.go:76).                    */
 typedef struct hs_device_info {
@@ -117,6 +127,7 @@ typedef struct hs_device_info {
   const hs_mig_profile* mig_profiles;   /* DeviceInfo.MIGProfiles (devices.go:141); read for mode "mig" only */
   uint32_t    n_mig_profiles;
   const hs_enflame_info* enflame;       /* HS_FIT_ENFLAME_VGCU devices only; NULL = no CustomInfo                */
+  const hs_metax_sgpu_info* sgpu;       /* HS_FIT_METAX_SGPU devices only; NULL = no CustomInfo                  */
 } hs_device_info;
 
 /* device.NodeInfo (pkg/device/devices.go:170-174) plus the node annotations the
@@ -319,7 +330,29 @@ enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
         * gcu-assigned-time (returned empty), gcu-assigned-index / -id / -minor and gcu-request-size of the first
         * container with a device, assigned-containers = {"<container name>": {"allocated":false,"request":<slices>,
         * "profileID":…,"profileName":…}} (hs_container.name).                                                          */
-       HS_FIT_ENFLAME_VGCU = 10 };
+       HS_FIT_ENFLAME_VGCU = 10,
+       /* metax sGPU, type "Metax-SGPU" (pkg/device/metax/sdevice.go:295-495).  Filter, then prioritise.  A device passes
+        * when it is healthy ("CardUnhealthy"), its application class agrees with the pod's
+        * metax-tech.com/sgpu-app-class (a device in use runs either online/offline pods or plain ones, and an offline pod
+        * never joins a device with online pods: "CardAppClassMismatch"), — unless the pod is online — its QoS policy
+        * agrees with metax-tech.com/sgpu-qos-policy (an idle device and an exclusive request always pass; the device's
+        * policy is the one a previous Filter is switching it to, if any, else the registered one:
+        * "CardQosPolicyMismatch"), then uuid lists (metax-tech.com/use-gpuuuid / nouse-gpuuuid), slots, mutex, memory
+        * and — unless online — cores, exclusivity and exhaustion as in the template.  Fewer passing devices than asked:
+        * no fit.  More: an online pod takes the devices with the fewest online, then offline, pods (devices that only run
+        * offline pods last); a request for whole cards (Coresreq 100, no app class) takes a MetaLink zone that holds
+        * enough of them (the smallest such zone; equal sizes in ascending zone), else fills up across zones, then with
+        * unlinked devices; everything else the first ones in list order.  An online pod's picks record 0 cores.
+        * ScoreNode (:295-304) is policy neutral — OverrideScore multiplies it by 10000, or -10000 under node policy
+        * "spread" (policy/node_policy.go:82-88): online pods lose 100 per offline pod on a picked device that runs only
+        * offline pods, else 20 per online and 2 per offline pod; whole-card pods with topology awareness (the vendor's
+        * `option`, overridden by metax-tech.com/sgpu-topology-aware) score 10 x the MetaLink pairs among their cards minus
+        * the pairs the node loses (:669-...).  Annotations: both hami keys, metax-tech.com/gpu-devices-allocated (JSON),
+        * metax-tech.com/predicate-time (returned empty).  The engine keeps the class counts and the pending QoS switches
+        * per device; hs_node_upsert of a device whose registered policy equals its pending one retires the switch
+        * (JitteryQosCache.Sync, metax/qos.go:37-59).  Pods reach the cache with their class through hs_filter or
+        * hs_pod_ingest (the annotations are read there); hs_usage_apply adds classless pods.                             */
+       HS_FIT_METAX_SGPU = 11 };
 typedef struct hs_vendor_config {
   const char* common_word;       /* DevicesMap key == k.Type == DeviceInfo.DeviceVendor                     */
   int32_t     fit_kind;          /* HS_FIT_*                                                                  */
@@ -329,6 +362,7 @@ typedef struct hs_vendor_config {
   const char* allocated_key;     /* SupportDevices[word];   NULL = "hami.io/<word>-devices-allocated"         */
   const char* use_type_key;      /* HS_FIT_AMD: "amd.com/use-gputype" / "amd.com/nouse-gputype"; NULL = no lists */
   const char* nouse_type_key;
+  int32_t     option;            /* HS_FIT_METAX_SGPU: 1 = MetaxConfig.TopologyAware (sgpuTopologyAware); else 0          */
 } hs_vendor_config;
 
 typedef struct hs_config {
@@ -447,6 +481,7 @@ typedef struct hs_quantity {
   uint8_t     as_int64_ok;  /* … and its ok flag                            */
   int64_t     value;        /* Quantity.Value()                             */
   int8_t      sign;         /* Quantity.Sign()                              */
+  uint8_t     has_suffix;   /* Quantity.String() contains a letter (a unit): read by HS_REQ_METAX_SGPU only */
 } hs_quantity;
 typedef struct hs_container_resources {
   const hs_quantity* limits;   uint32_t n_limits;     /* ctr.Resources.Limits   */
@@ -461,6 +496,8 @@ enum { HS_REQ_NVIDIA = 0, HS_REQ_DCU = 1, HS_REQ_MLU = 2, HS_REQ_ASCEND = 3,
        HS_REQ_METAX = 9,      /* metax/device.go:134-154: Memreq 0, MemPercentagereq 100, Coresreq 100            */
        HS_REQ_KUNLUN_VXPU = 11, /* kunlun/vdevice.go:173-213: count + memory trimmed up to 24576 / 49152 / 98304 MiB, cores =
                                * the memory's share of a card in percent; no memory = the whole card                 */
+       HS_REQ_METAX_SGPU = 13,/* metax/sdevice.go:222-293: Limits only; cores default 100; memory in Gi unless the quantity carries a
+                               * unit (hs_quantity.has_suffix), then MiB                                                  */
        HS_REQ_ENFLAME = 12,   /* enflame/device.go:322-366: count_name (enflame.com/drs-gcu) > 0 = a direct slice request (Nums 1,
                                * Memreq = the count, MemPercentagereq 0); else memory_name / cores_name by spec (Nums 1,
                                * Memreq, Coresreq, MemPercentagereq -1); Quantity.Value() of Limits, then Requests        */
@@ -497,6 +534,8 @@ enum { HS_REG_CSV = 0,    /* device.DecodeNodeDevices  (pkg/device/devices.go:31
                                       * .scores values or NULL (hs_node_register hands them to hs_node_info)            */
        HS_REG_CAPACITY_KUNLUN = 6,   /* kunlun/device.go:64-91: capacity_cores = the XPU count, <node>-kunlun-<i>, Count 100,
                                       * 98304 MiB, the upper half of the cards on NUMA 1                                */
+       HS_REG_METAX_SGPU = 8,        /* metax/sdevice.go:506-526 + protocol.go:96-116: `annotation` = the node's
+                                      * metax-tech.com/node-gpu-devices JSON ([]MetaxSDeviceInfo); Index = position             */
        HS_REG_ENFLAME_DRS = 7,       /* enflame/device.go:198-252: `annotation` = the node's enflame.com/gcu-drs-capacity JSON
                                       * {"devices":[{"index","minor","capacity"}],"profiles":{name:id}}; <node>-enflame-drs-<i>,
                                       * Count = capacity, Devmem = the largest profile's GB * 1024, Devcore 100            */

@@ -27,6 +27,10 @@ class hs_enflame_info(C.Structure):
                 ("profiles", C.POINTER(hs_kv)), ("n_profiles", C.c_uint32)]
 
 
+class hs_metax_sgpu_info(C.Structure):
+    _fields_ = [("qos_policy", C.c_char_p), ("link_zone", C.c_int32)]
+
+
 class hs_mig_placement(C.Structure):
     _fields_ = [("start", C.c_uint32), ("size", C.c_uint32)]
 
@@ -45,7 +49,16 @@ class hs_device_info(C.Structure):
                 ("devcore", C.c_int32), ("type", C.c_char_p), ("numa", C.c_int32), ("mode", C.c_char_p),
                 ("health", C.c_uint8), ("vendor", C.c_char_p), ("network_id", C.c_int32),
                 ("mig_profiles", C.POINTER(hs_mig_profile)), ("n_mig_profiles", C.c_uint32),
-                ("enflame", C.POINTER(hs_enflame_info))]
+                ("enflame", C.POINTER(hs_enflame_info)), ("sgpu", C.POINTER(hs_metax_sgpu_info))]
+
+
+def build_sgpu_info(info, keep):
+    """{"qos_policy", "link_zone"} -> POINTER(hs_metax_sgpu_info) or None"""
+    if info is None:
+        return None
+    e = hs_metax_sgpu_info(_b(info.get("qos_policy", "")), int(info.get("link_zone", 0)))
+    keep.append(e)
+    return C.pointer(e)
 
 
 def build_enflame_info(info, keep):
@@ -110,7 +123,7 @@ class hs_sim_node(C.Structure):
 
 
 HS_REG_CSV, HS_REG_JSON, HS_REG_CAPACITY_MLU, HS_REG_CAPACITY_MTHREADS, HS_REG_CAPACITY_METAX, HS_REG_CAPACITY_NEURON = 0, 1, 2, 3, 4, 5
-HS_REG_CAPACITY_KUNLUN, HS_REG_ENFLAME_DRS = 6, 7
+HS_REG_CAPACITY_KUNLUN, HS_REG_ENFLAME_DRS, HS_REG_METAX_SGPU = 6, 7, 8
 
 
 class hs_container_request(C.Structure):
@@ -163,7 +176,8 @@ class hs_ascend_config(C.Structure):
 
 
 class hs_quantity(C.Structure):
-    _fields_ = [("name", C.c_char_p), ("as_int64", C.c_int64), ("as_int64_ok", C.c_uint8), ("value", C.c_int64), ("sign", C.c_int8)]
+    _fields_ = [("name", C.c_char_p), ("as_int64", C.c_int64), ("as_int64_ok", C.c_uint8), ("value", C.c_int64), ("sign", C.c_int8),
+                ("has_suffix", C.c_uint8)]
 
 
 class hs_container_resources(C.Structure):
@@ -178,17 +192,17 @@ class hs_vendor_resources(C.Structure):
 
 HS_REQ_NVIDIA, HS_REQ_DCU, HS_REQ_MLU, HS_REQ_ASCEND = 0, 1, 2, 3
 HS_REQ_ILUVATAR, HS_REQ_COUNT, HS_REQ_AMD, HS_REQ_MTHREADS, HS_REQ_WHOLE_CARD, HS_REQ_METAX, HS_REQ_NEURON = 4, 5, 6, 7, 8, 9, 10
-HS_REQ_KUNLUN_VXPU, HS_REQ_ENFLAME = 11, 12
+HS_REQ_KUNLUN_VXPU, HS_REQ_ENFLAME, HS_REQ_METAX_SGPU = 11, 12, 13
 
 
 class hs_vendor_config(C.Structure):
     _fields_ = [("common_word", C.c_char_p), ("fit_kind", C.c_int32), ("use_uuid_key", C.c_char_p),
                 ("nouse_uuid_key", C.c_char_p), ("to_allocate_key", C.c_char_p), ("allocated_key", C.c_char_p),
-                ("use_type_key", C.c_char_p), ("nouse_type_key", C.c_char_p)]
+                ("use_type_key", C.c_char_p), ("nouse_type_key", C.c_char_p), ("option", C.c_int32)]
 
 
 HS_FIT_TEMPLATE, HS_FIT_COUNT_ONLY, HS_FIT_AMD, HS_FIT_MTHREADS, HS_FIT_WHOLE_CARD, HS_FIT_METAX, HS_FIT_NEURON, HS_FIT_VASTAI = 0, 1, 2, 3, 4, 5, 6, 7
-HS_FIT_KUNLUN, HS_FIT_KUNLUN_VXPU, HS_FIT_ENFLAME_VGCU = 8, 9, 10
+HS_FIT_KUNLUN, HS_FIT_KUNLUN_VXPU, HS_FIT_ENFLAME_VGCU, HS_FIT_METAX_SGPU = 8, 9, 10, 11
 
 # The plain-Fit vendors of the reference's default device config: iluvatar's CommonWords
 # (pkg/scheduler/config/config.go iluvatars: BI-V100 / BI-V150 / MR-V100 / MR-V50) and biren (biren/device.go:40-47).
@@ -216,6 +230,9 @@ DEFAULT_VENDORS = [
     # kunlun whole XPUs (kunlun/device.go:32-56): SupportDevices only; the second uuid pair (baidu.com/...) is fixed in the Fit
     ("kunlun", HS_FIT_KUNLUN, "hami.io/use-xpu-uuid", "hami.io/no-use-xpu-uuid", None, "hami.io/kunlun-allocated"),
     # kunlun shared XPUs (kunlun/vdevice.go:34-63)
+    # metax sGPU (metax/sdevice.go:39-46,63-84); option = MetaxConfig.TopologyAware
+    ("Metax-SGPU", HS_FIT_METAX_SGPU, "metax-tech.com/use-gpuuuid", "metax-tech.com/nouse-gpuuuid",
+     "hami.io/metax-sgpu-devices-to-allocate", "hami.io/metax-sgpu-devices-allocated", None, None, 0),
     # enflame shared vGCU (enflame/device.go:38-46,86-104): SupportDevices only
     ("Enflame", HS_FIT_ENFLAME_VGCU, "enflame.com/use-gpuuuid", "enflame.com/nouse-gpuuuid", None, "hami.io/enflame-vgpu-devices-allocated"),
     ("XPU", HS_FIT_KUNLUN_VXPU, "hami.io/use-xpu-uuid", "hami.io/no-use-xpu-uuid", "hami.io/xpu-devices-to-allocate",
@@ -260,7 +277,8 @@ def build_config(node_policy=None, gpu_policy=None, ascend=None, ascend_hami_vnp
     for i, v in enumerate(vendors):
         word, kind, use, nouse, toalloc, alloc = v[:6]
         use_t, nouse_t = (v[6], v[7]) if len(v) > 6 else (None, None)
-        varr[i] = hs_vendor_config(_b(word), kind, _b(use), _b(nouse), _b(toalloc), _b(alloc), _b(use_t), _b(nouse_t))
+        varr[i] = hs_vendor_config(_b(word), kind, _b(use), _b(nouse), _b(toalloc), _b(alloc), _b(use_t), _b(nouse_t),
+                                   int(v[8]) if len(v) > 8 else 0)
     keep.append(varr)
     ascend = DEFAULT_ASCEND if ascend is None else ascend
     arr = (hs_ascend_config * max(1, len(ascend)))()
@@ -292,7 +310,8 @@ def build_node(node):
         arr[i] = hs_device_info(_b(d["id"]), d.get("index", i), d.get("count", 0), d.get("devmem", 0),
                                 d.get("devcore", 0), _b(d.get("type", "")), d.get("numa", 0), _b(d.get("mode", "")),
                                 1 if d.get("health", True) else 0, _b(d.get("vendor", "NVIDIA")),
-                                d.get("network_id", -1), mp, nmp, build_enflame_info(d.get("enflame"), keep))
+                                d.get("network_id", -1), mp, nmp, build_enflame_info(d.get("enflame"), keep),
+                                build_sgpu_info(d.get("sgpu"), keep))
     ps = None
     if node.get("pair_scores") is not None:
         n = len(devs)

@@ -314,9 +314,9 @@ struct hs_handle {
   bool shard_use_nccl = false;               // HS_SHARD_NCCL=1: keep the launch-per-decision NCCL baseline
   uint32_t epoch_base = 0;
   bool force_shard = false;  // HS_FORCE_SHARD=1: run the sharded pipeline (sweep / decide / explain kernels) with world == 1
-  struct FailTab { uint32_t k0, k1, k2; const std::string* s; };
+  struct FailTab { uint32_t k0, k1, k2, k3; const std::string* s; };
   static constexpr uint32_t kFailTab = 8192;
-  std::vector<FailTab> fail_tab = std::vector<FailTab>(kFailTab, FailTab{0, 0, 0, nullptr});
+  std::vector<FailTab> fail_tab = std::vector<FailTab>(kFailTab, FailTab{0, 0, 0, 0, nullptr});
   // device.QuotaManager (quota.go): (namespace, vendor id) -> {memory, cores}; Used is tracked for every namespace
   // (addUsageLocked auto-creates entries), rows with a limit set travel to the device with each batch
   struct QuotaEnt { int64_t limit[2] = {0, 0}; bool set[2] = {false, false}; int64_t used[2] = {0, 0}; };
@@ -376,7 +376,7 @@ struct hs_handle {
   std::string r_buf;                    // device-list annotation of the last assembled result
   DevFail last_fail = {0xffffffffu, 0, 0, 0};
   const std::string* last_fail_str = nullptr;
-  std::map<std::array<uint32_t, 3>, std::string> reason_cache;
+  std::map<std::array<uint32_t, 4>, std::string> reason_cache;
 
   const char* keep(const std::string& s) { r_strs.push_back(s); return r_strs.back().c_str(); }
 };
@@ -396,7 +396,8 @@ static const char* kReasonNames[HS_R_COUNT] = {
     "CardTypeMismatch", "CardUuidMismatch", "CardTimeSlicingExhausted", "CardComputeUnitsExhausted",
     "CardInsufficientMemory", "CardInsufficientCore", "CardNotHealth", "CardCordoned", "NumaNotFit",
     "ExclusiveDeviceAllocateConflict", "CardNotFoundCustomFilterRule", "CardMigTopologyInfeasible",
-    "AllocatedCardsInsufficientRequest", "ResourceQuotaNotFit", "ModeNotFit"};
+    "AllocatedCardsInsufficientRequest", "ResourceQuotaNotFit", "ModeNotFit",
+    "CardUnhealthy", "CardAppClassMismatch", "CardQosPolicyMismatch"};
 
 void add_vendor(hs_handle* h, const std::string& word, bool ascend) {
   VendorInfo v;
@@ -1129,13 +1130,13 @@ inline const std::string& fail_string(hs_handle* h, const DevFail& f) {
   // node: a direct-mapped table of reason records in front of the map (references into the map stay valid)
   const uint32_t hsh = (f.kind_cards * 0x9E3779B1u) ^ (f.c0 * 0x85EBCA6Bu) ^ (f.c1 * 0xC2B2AE35u);
   hs_handle::FailTab& t = h->fail_tab[(hsh >> 16) & (hs_handle::kFailTab - 1)];
-  if (t.s && t.k0 == f.kind_cards && t.k1 == f.c0 && t.k2 == f.c1) return *t.s;
+  if (t.s && t.k0 == f.kind_cards && t.k1 == f.c0 && t.k2 == f.c1 && t.k3 == f.pad) return *t.s;
   const std::string& s = fail_string_slow(h, f);
-  t.k0 = f.kind_cards; t.k1 = f.c0; t.k2 = f.c1; t.s = &s;
+  t.k0 = f.kind_cards; t.k1 = f.c0; t.k2 = f.c1; t.k3 = f.pad; t.s = &s;
   return s;
 }
 const std::string& fail_string_slow(hs_handle* h, const DevFail& f) {
-  std::array<uint32_t, 3> key = {f.kind_cards, f.c0, f.c1};
+  std::array<uint32_t, 4> key = {f.kind_cards, f.c0, f.c1, f.pad};
   auto it = h->reason_cache.find(key);
   if (it != h->reason_cache.end()) return it->second;
   std::string s;
@@ -1152,7 +1153,7 @@ const std::string& fail_string_slow(hs_handle* h, const DevFail& f) {
     std::vector<std::string> parts;
     char buf[96];
     for (int r = 0; r < HS_R_COUNT; r++) {
-      uint32_t cnt = r < 8 ? (f.c0 >> (4 * r)) & 15u : (f.c1 >> (4 * (r - 8))) & 15u;
+      uint32_t cnt = r < 8 ? (f.c0 >> (4 * r)) & 15u : (r < 16 ? (f.c1 >> (4 * (r - 8))) & 15u : (f.pad >> (4 * (r - 16))) & 15u);
       if (!cnt) continue;
       snprintf(buf, sizeof buf, "%u/%u %s", cnt, cards, kReasonNames[r]);
       parts.push_back(buf);

@@ -32,7 +32,7 @@ struct EvalOut {
   uint32_t n_alloc;
   // EV_EXPLAIN
   uint32_t fkind, fcards;
-  uint32_t reasons[16];
+  uint32_t reasons[24];
 };
 
 __device__ __forceinline__ int ord_get(uint32_t order, int i) { return (order >> (4 * i)) & 7; }
@@ -242,7 +242,7 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
   bool needTopology = isNv && (pod.flags & PF_TOPOLOGY);
   const bool isHAMiCore = isAscend && (pod.flags & PF_ASCEND_HAMICORE);
   if (MODE == EV_EXPLAIN) {
-    for (int r = 0; r < 16; r++) out.reasons[r] = 0;
+    for (int r = 0; r < 24; r++) out.reasons[r] = 0;
     out.fkind = FK_HIST;
     out.fcards = (uint32_t)cnt;
   }

@@ -148,9 +148,12 @@ __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
   uint32_t c0 = 0, c1 = 0;
   if (out.fkind == FK_HIST) {
     for (int r = 0; r < 8; r++) c0 |= (out.reasons[r] & 15u) << (4 * r);
-    for (int r = 8; r < 15; r++) c1 |= (out.reasons[r] & 15u) << (4 * (r - 8));
+    for (int r = 8; r < 16; r++) c1 |= (out.reasons[r] & 15u) << (4 * (r - 8));
   }
-  f.c0 = c0; f.c1 = c1; f.pad = 0;
+  uint32_t c2 = 0;
+  if (out.fkind == FK_HIST)
+    for (int r = 16; r < 24; r++) c2 |= (out.reasons[r] & 15u) << (4 * (r - 16));
+  f.c0 = c0; f.c1 = c1; f.pad = c2;
 }
 // FK_MIG_ADD_FAILED names a device of the node in its text: the node slot rides along (fcards holds the device slot)
 __device__ __forceinline__ void pack_fail_node(const EvalOut& out, DevFail& f, int node) {

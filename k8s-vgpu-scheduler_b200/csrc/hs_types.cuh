@@ -228,8 +228,8 @@ enum { FK_NONE = 0, FK_HIST = 1, FK_NODE_INSUFFICIENT = 2, FK_TYPE_NOT_FOUND = 3
 struct DevFail {            // 16 B
   uint32_t kind_cards;      // bits0-3 kind | bits4-31 cards denominator
   uint32_t c0;              // reasons 0-7, 4 bits each (HS_R_* order)
-  uint32_t c1;              // reasons 8-14
-  uint32_t pad;
+  uint32_t c1;              // reasons 8-15
+  uint32_t pad;             // reasons 16-23 (metax sGPU's CardUnhealthy / CardAppClassMismatch / CardQosPolicyMismatch); FK_HIST only
 };
 
 // one 16 B slot per op: the arg-best key and the grid barrier that publishes it share an L2 sector

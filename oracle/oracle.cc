@@ -1298,6 +1298,177 @@ FitResult fitEnflame(const std::vector<DeviceUsage*>& devices, const ContainerDe
   return r;
 }
 
+// ---- metax sGPU ("Metax-SGPU", metax/sdevice.go:295-495): filter, then prioritise ------------------------------------
+struct SgpuState {                      // the vendor object's jqCache (metax/qos.go): device UUID -> the QoS it is about to switch to
+  std::map<std::string, std::string> jq;
+};
+static const std::string* podAnno(const Pod& pod, const char* key) { return anno(pod, key); }
+static bool sgpuCheckAppClass(const std::string& requestClass, const DeviceUsage& dev) {    // checkAppClass, sdevice.go:664-703
+  if (dev.Used == 0) return true;
+  const bool devOnline = dev.OnlinePods > 0, devOffline = dev.OfflinePods > 0;
+  if ((devOffline || devOnline) == (requestClass == "offline" || requestClass == "online")) {
+    if (devOnline && requestClass == "offline") return false;
+    return true;
+  }
+  return false;
+}
+static bool sgpuCheckQos(const SgpuState& st, const std::string& reqQos, const DeviceUsage& usage, const ContainerDeviceRequest& request) {   // :527-556
+  if (usage.Used == 0) return true;
+  if (request.Coresreq == 100) return true;
+  std::string devQos;
+  auto it = st.jq.find(usage.ID);
+  if (it != st.jq.end()) devQos = it->second;
+  else if (usage.HasSgpu) devQos = usage.QosPolicy;
+  return devQos == "" || reqQos == devQos;
+}
+// prioritizeOnlineDevices, :717-770: sort.Slice on <= 12 candidates is Go's insertion sort
+static std::vector<DeviceUsage*> sgpuPrioritizeOnline(std::vector<DeviceUsage*> c, int require) {
+  if ((int)c.size() <= require) return c;
+  auto less = [](const DeviceUsage* a, const DeviceUsage* b) {
+    const bool iOnly = a->OnlinePods == 0 && a->OfflinePods > 0, jOnly = b->OnlinePods == 0 && b->OfflinePods > 0;
+    if (iOnly && jOnly) return a->OfflinePods < b->OfflinePods;
+    if (iOnly) return false;
+    if (jOnly) return true;
+    if (a->OnlinePods == b->OnlinePods) return a->OfflinePods < b->OfflinePods;
+    return a->OnlinePods < b->OnlinePods;
+  };
+  for (size_t i = 1; i < c.size(); i++)
+    for (size_t j = i; j > 0 && less(c[j], c[j - 1]); j--) std::swap(c[j], c[j - 1]);
+  c.resize(require);
+  return c;
+}
+// prioritizeExclusiveDevices, :583-645.  The MetaLink groups come out of a Go map: taken in ascending link zone (canonical
+// rule), then ordered by size with Go's insertion sort.
+static std::vector<DeviceUsage*> sgpuPrioritizeExclusive(const std::vector<DeviceUsage*>& cand, int require) {
+  if ((int)cand.size() <= require) return cand;
+  std::map<int32_t, std::vector<DeviceUsage*>> byZone;
+  for (auto d : cand) byZone[d->HasSgpu ? d->LinkZone : 0].push_back(d);
+  std::vector<std::vector<DeviceUsage*>> link;
+  std::vector<DeviceUsage*> other;
+  for (auto& kv : byZone) {
+    if (kv.first <= 0) other.insert(other.end(), kv.second.begin(), kv.second.end());
+    else link.push_back(kv.second);
+  }
+  for (size_t i = 1; i < link.size(); i++)
+    for (size_t j = i; j > 0 && link[j].size() < link[j - 1].size(); j--) std::swap(link[j], link[j - 1]);
+  for (auto& g : link)
+    if ((int)g.size() >= require) return std::vector<DeviceUsage*>(g.begin(), g.begin() + require);
+  std::vector<DeviceUsage*> out;
+  for (auto& g : link)
+    for (auto d : g) { out.push_back(d); if ((int)out.size() >= require) return out; }
+  for (auto d : other) { out.push_back(d); if ((int)out.size() >= require) return out; }
+  return std::vector<DeviceUsage*>(cand.begin(), cand.begin() + require);
+}
+FitResult fitSgpu(const SgpuState& st, const std::vector<DeviceUsage*>& devices, const ContainerDeviceRequest& request, const Pod& pod,
+                  const std::string& gpuPolicyDefault) {
+  std::map<std::string, int> reason;
+  const bool isMutex = PolicyContains(GetGPUSchedulerPolicyByPod(gpuPolicyDefault, pod), "mutex");
+  const std::string* classAnno = podAnno(pod, "metax-tech.com/sgpu-app-class");
+  const std::string appClass = classAnno ? *classAnno : "";
+  const std::string* qosAnno = podAnno(pod, "metax-tech.com/sgpu-qos-policy");
+  const std::string reqQos = qosAnno ? *qosAnno : "";
+  std::vector<DeviceUsage*> candidates;
+  for (int i = (int)devices.size() - 1; i >= 0; i--) {
+    DeviceUsage* dev = devices[i];
+    if (request.Type != "Metax-SGPU") { reason["CardTypeMismatch"]++; continue; }
+    if (!dev->Health) { reason["CardUnhealthy"]++; continue; }
+    if (!sgpuCheckAppClass(appClass, *dev)) { reason["CardAppClassMismatch"]++; continue; }
+    if (appClass != "online" && !sgpuCheckQos(st, reqQos, *dev, request)) { reason["CardQosPolicyMismatch"]++; continue; }
+    if (!CheckUUID(pod.Annotations, dev->ID, "metax-tech.com/use-gpuuuid", "metax-tech.com/nouse-gpuuuid")) { reason["CardUuidMismatch"]++; continue; }
+    if (dev->Count <= dev->Used) { reason["CardTimeSlicingExhausted"]++; continue; }
+    if (isMutex && dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+    int32_t memreq = request.Memreq > 0 ? request.Memreq : i32mul(dev->Totalmem, request.MemPercentagereq) / 100;
+    if (i32sub(dev->Totalmem, dev->Usedmem) < memreq) { reason["CardInsufficientMemory"]++; continue; }
+    if (appClass != "online") {
+      if (i32sub(dev->Totalcore, dev->Usedcores) < request.Coresreq) { reason["CardInsufficientCore"]++; continue; }
+      if (dev->Totalcore == 100 && request.Coresreq == 100 && dev->Used > 0) { reason["ExclusiveDeviceAllocateConflict"]++; continue; }
+      if (dev->Totalcore != 0 && dev->Usedcores == dev->Totalcore && request.Coresreq == 0) { reason["CardComputeUnitsExhausted"]++; continue; }
+    }
+    candidates.push_back(dev);
+  }
+  FitResult r;
+  if ((int)candidates.size() < (int)request.Nums) {
+    if (!candidates.empty()) reason["AllocatedCardsInsufficientRequest"] = (int)candidates.size();
+    r.fit = false; r.reason = GenReason(reason, (int)devices.size());
+    return r;
+  }
+  const int nums = request.Nums < 0 ? 0 : (int)request.Nums;
+  std::vector<DeviceUsage*> best(candidates.begin(), candidates.begin() + nums);
+  if ((int)candidates.size() > nums) {
+    if (classAnno) { if (appClass == "online") best = sgpuPrioritizeOnline(candidates, nums); }
+    else if (request.Coresreq == 100) best = sgpuPrioritizeExclusive(candidates, nums);
+  }
+  const int32_t coreReq = appClass == "online" ? 0 : request.Coresreq;
+  for (auto dev : best) {
+    ContainerDevice cd;
+    cd.Idx = (int)dev->Index; cd.UUID = dev->ID; cd.Type = dev->Type;
+    cd.Usedmem = request.Memreq > 0 ? request.Memreq : i32mul(dev->Totalmem, request.MemPercentagereq) / 100;
+    cd.Usedcores = coreReq;
+    cd.HasSgpu = dev->HasSgpu; cd.SgpuQos = dev->QosPolicy; cd.SgpuLinkZone = dev->LinkZone; cd.PodAnnotations = &pod.Annotations;
+    r.devs.push_back(cd);
+  }
+  r.fit = true;
+  return r;
+}
+// LinkDevices.Score, metax/score.go:27-57
+static int sgpuLinkScore(const std::vector<std::pair<std::string, int32_t>>& devs) {
+  int score = 0;
+  for (size_t i = 0; i < devs.size(); i++)
+    for (size_t j = i + 1; j < devs.size(); j++)
+      if (devs[i].first != devs[j].first && devs[i].second != 0 && devs[j].second != 0 && devs[i].second == devs[j].second) score += 10;
+  return score;
+}
+static float sgpuScoreNode(bool topoDefault, const PodSingleDevice& podDevices, const std::vector<DeviceUsage>* previous) {   // sdevice.go:295-304
+  static const std::vector<DeviceUsage> none;
+  const std::vector<DeviceUsage>& prev = previous ? *previous : none;
+  bool online = false;                                              // appClassOnlineEnable, :705-715
+  for (auto& ctr : podDevices)
+    for (auto& d : ctr)
+      if (d.PodAnnotations) { auto it = d.PodAnnotations->find("metax-tech.com/sgpu-app-class"); if (it != d.PodAnnotations->end() && it->second == "online") online = true; }
+  if (online) {                                                     // scoreOnlineDevices, :772-811
+    std::set<std::string> deviceSet;
+    for (auto& ctr : podDevices) for (auto& d : ctr) deviceSet.insert(d.UUID);
+    int result = 0;
+    for (auto& dev : prev) {
+      if (!deviceSet.count(dev.ID)) continue;
+      if (dev.OfflinePods > 0 && dev.OnlinePods == 0) result += -100 * dev.OfflinePods;
+      else result += -20 * dev.OnlinePods - 2 * dev.OfflinePods;
+    }
+    return (float)result;
+  }
+  bool topo = false, decided = false;                               // topologyAwareEnable, :647-667: the FIRST exclusive pick decides
+  for (auto& ctr : podDevices) {
+    for (auto& d : ctr) {
+      if (d.Usedcores != 100) continue;
+      topo = topoDefault;
+      if (d.PodAnnotations) {
+        auto it = d.PodAnnotations->find("metax-tech.com/sgpu-topology-aware");
+        bool b;
+        if (it != d.PodAnnotations->end() && ParseBool(it->second, b)) topo = b;
+      }
+      decided = true;
+      break;
+    }
+    if (decided) break;
+  }
+  if (!topo) return 0;
+  std::vector<std::pair<std::string, int32_t>> available, allocated, rest;     // scoreExclusiveDevices
+  for (auto& ctr : podDevices)
+    for (auto& d : ctr)
+      if (d.Usedcores == 100) allocated.emplace_back(d.UUID, d.HasSgpu ? d.SgpuLinkZone : 0);
+  for (auto& dev : prev) {
+    if (dev.Used != 0) continue;
+    const int32_t zone = dev.HasSgpu ? dev.LinkZone : 0;
+    available.emplace_back(dev.ID, zone);
+    bool find = false;
+    for (auto& a : allocated) if (a.first == dev.ID) { find = true; break; }
+    if (!find) rest.emplace_back(dev.ID, zone);
+  }
+  const int availableScore = sgpuLinkScore(available), allocatedScore = sgpuLinkScore(allocated), restScore = sgpuLinkScore(rest);
+  const int lossScore = availableScore - allocatedScore - restScore;
+  return (float)(10 * allocatedScore - lossScore);
+}
+
 // iluvatar (one instance per CommonWord, iluvatar/device.go:60-83) and biren (biren/device.go:54-66)
 class PlainDevices : public Devices {
  public:
@@ -1308,6 +1479,7 @@ class PlainDevices : public Devices {
                 const QuotaManager* quota) const override {
     static const Vendor kinds[] = {Vendor::PLAIN, Vendor::COUNT_ONLY, Vendor::AMD, Vendor::MTHREADS, Vendor::WHOLE_CARD, Vendor::METAX,
                                    Vendor::PLAIN /* 6 = Neuron, below */, Vendor::VASTAI};
+    if (v_.FitKind == 11) return fitSgpu(sgpu_, devices, request, pod, def);
     if (v_.FitKind == 10) return fitEnflame(devices, request, pod, def);
     if (v_.FitKind == 8 || v_.FitKind == 9) return fitKunlun(v_.CommonWord, devices, request, pod, v_.FitKind == 9, def);
     FitGates g{kinds[v_.FitKind >= 0 && v_.FitKind <= 7 ? v_.FitKind : 0],
@@ -1317,6 +1489,17 @@ class PlainDevices : public Devices {
     return fitTemplate(g, devices, request, pod, nodeInfo, def, allocated, quota, GetResourceNames());
   }
   bool AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const override {
+    if (v_.FitKind == 11) {                                                // metax/sdevice.go:310-330
+      Devices::AddResourceUsage(n, ctr);
+      const std::string* cls = ctr.PodAnnotations ? (ctr.PodAnnotations->count("metax-tech.com/sgpu-app-class") ? &ctr.PodAnnotations->at("metax-tech.com/sgpu-app-class") : nullptr) : nullptr;
+      if (!(cls && *cls == "online") && n.HasSgpu) {
+        std::string expectedQos;
+        if (ctr.PodAnnotations) { auto q = ctr.PodAnnotations->find("metax-tech.com/sgpu-qos-policy"); if (q != ctr.PodAnnotations->end()) expectedQos = q->second; }
+        if (ctr.Usedcores == 100) expectedQos = "";
+        n.QosPolicy = expectedQos;        // the working copy's CustomInfo["QosPolicy"]
+      }
+      return true;
+    }
     if (v_.FitKind == 8) { n.Used = i32add(n.Used, 1); return true; }      // kunlun/device.go:179-182: the slot only
     if (v_.FitKind == 10) {                                                // enflame/device.go:372-380: the slot count grows by the slice size
       int slice = ctr.DrsSlice <= 0 ? 1 : ctr.DrsSlice;
@@ -1336,6 +1519,7 @@ class PlainDevices : public Devices {
   // metax/device.go:185-214: 2000 minus the node's topology loss (binpack) / score (spread) for this many devices
   float ScoreNode(const PodSingleDevice& podDevices, const std::string& policy, const NodeInfo* nodeInfo,
                   const std::vector<DeviceUsage>* previous) const override {
+    if (v_.FitKind == 11) return sgpuScoreNode(v_.Option != 0, podDevices, previous);
     if (v_.FitKind == 8) {            // kunlun/device.go:154-177
       std::vector<int> current, prev;
       auto addidx = [](std::vector<int>& t, int v) { if (std::find(t.begin(), t.end(), v) == t.end()) t.push_back(v); };
@@ -1404,6 +1588,39 @@ class PlainDevices : public Devices {
         }
         return;
       }
+      if (v_.FitKind == 11) {
+        // metax/sdevice.go:142-171: both hami keys, the pod's devices in metax's own JSON, a timestamp (blanked), and the
+        // side effect that makes the next Filter see a QoS switch in flight (addJitteryQos, :558-581)
+        annos[v_.ToAllocate] = s;
+        annos[v_.Allocated] = s;
+        std::string js = "[";
+        for (size_t c = 0; c < it->second.size(); c++) {
+          js += c ? ",[" : "[";
+          for (size_t d = 0; d < it->second[c].size(); d++) {
+            const ContainerDevice& cd = it->second[c][d];
+            js += d ? ",{" : "{";
+            js += "\"uuid\":" + jsonString(cd.UUID);
+            if (cd.Usedcores != 0) js += ",\"compute\":" + std::to_string(cd.Usedcores);
+            if (cd.Usedmem != 0) js += ",\"vRam\":" + std::to_string(cd.Usedmem);
+            js += "}";
+          }
+          js += "]";
+        }
+        annos["metax-tech.com/gpu-devices-allocated"] = js + "]";
+        annos["metax-tech.com/predicate-time"] = "";
+        const std::string* cls = anno(pod, "metax-tech.com/sgpu-app-class");
+        if (!(cls && *cls == "online")) {
+          const std::string* q = anno(pod, "metax-tech.com/sgpu-qos-policy");
+          const std::string reqQos = q ? *q : "";
+          for (auto& ctrdev : it->second)
+            for (auto& dev : ctrdev) {
+              if (!dev.HasSgpu) continue;
+              const std::string expectedQos = dev.Usedcores == 100 ? "" : reqQos;
+              if (dev.SgpuQos != expectedQos) sgpu_.jq[dev.UUID] = expectedQos;
+            }
+        }
+        return;
+      }
       if (v_.FitKind == 10) {
         // enflame/device.go:254-300: the allocated key, gcu-assigned = "false", a timestamp (blanked, canonical rule 6), the
         // first container's index / minor / slice count, and assigned-containers = {container name: request} as JSON
@@ -1451,8 +1668,18 @@ class PlainDevices : public Devices {
     }
   }
 
+  bool PolicyNeutralScore() const override { return v_.FitKind == 11; }      // metax/sdevice.go:305-308
+  void SyncRegistered(const std::vector<DeviceInfo>& devices) const override {      // JitteryQosCache.Sync, metax/qos.go:37-59
+    if (v_.FitKind != 11) return;
+    for (auto& d : devices) {
+      auto it = sgpu_.jq.find(d.ID);
+      if (it != sgpu_.jq.end() && it->second == d.QosPolicy) sgpu_.jq.erase(it);
+    }
+  }
+
  private:
   Config::PlainVendor v_;
+  mutable SgpuState sgpu_;
 };
 
 class DCUDevices : public Devices {
@@ -1620,6 +1847,7 @@ const Devices* Scheduler::Vendor(const std::string& key) const {
 }
 
 void Scheduler::AddNode(const NodeInfo& info) {
+  for (auto& kv : info.Devices) { auto v = vendors_.find(kv.first); if (v != vendors_.end()) v->second->SyncRegistered(kv.second); }
   auto it = nodeIndex_.find(info.ID);
   std::vector<DeviceUsage> usage;
   for (auto& kv : info.Devices) {
@@ -1630,6 +1858,7 @@ void Scheduler::AddNode(const NodeInfo& info) {
       u.HasNetworkID = d.HasNetworkID; u.NetworkID = d.NetworkID;
       u.MigProfiles = d.MIGProfiles;   // scheduler.go:678
       u.EnfMinor = d.EnfMinor; u.EnfIndex = d.EnfIndex; u.EnfProfiles = d.EnfProfiles; u.EnfMaxSlice = d.EnfMaxSlice;   // CustomInfo, :684
+      u.HasSgpu = d.HasSgpu; u.QosPolicy = d.QosPolicy; u.LinkZone = d.LinkZone;
       usage.push_back(u);
     }
   }
@@ -1648,7 +1877,7 @@ void Scheduler::AddNode(const NodeInfo& info) {
     ne.usage = usage;
     ne.alive = true;
     for (auto& kv : pods_)
-      if (kv.second.NodeID == info.ID) applyUsage(ne, kv.second.Devices, +1);
+      if (kv.second.NodeID == info.ID) applyUsage(ne, kv.second.Devices, +1, kv.second.AppClass);
     refreshMig(ne);
   }
 }
@@ -1710,10 +1939,12 @@ bool Scheduler::AddPodWithMig(const std::string& uid, const std::string& ns, con
   auto it = nodeIndex_.find(node);
   if (it == nodeIndex_.end()) return false;
   auto old = pods_.find(uid);
+  std::string appClass;
   if (old != pods_.end()) {
+    appClass = old->second.AppClass;
     auto n = nodeIndex_.find(old->second.NodeID);
     if (n != nodeIndex_.end()) {
-      applyUsage(*nodes_[n->second], old->second.Devices, -1);
+      applyUsage(*nodes_[n->second], old->second.Devices, -1, old->second.AppClass);
       std::string prevNode = old->second.NodeID;
       pods_.erase(old);
       refreshMig(*nodes_[n->second]);
@@ -1722,9 +1953,9 @@ bool Scheduler::AddPodWithMig(const std::string& uid, const std::string& ns, con
     quota.AddUsage(ns, CountPodDevices(devices));
   }
   PodInfo pi;
-  pi.NodeID = node; pi.Namespace = ns; pi.Devices = devices; pi.MigAllocs = allocs;
+  pi.NodeID = node; pi.Namespace = ns; pi.Devices = devices; pi.MigAllocs = allocs; pi.AppClass = appClass;
   pods_[uid] = pi;
-  applyUsage(*nodes_[it->second], devices, +1);
+  applyUsage(*nodes_[it->second], devices, +1, appClass);
   refreshMig(*nodes_[it->second]);
   return true;
 }
@@ -1737,12 +1968,14 @@ bool Scheduler::RemoveNode(const std::string& name) {
 }
 
 // The usage a cached pod contributes: scheduler.go:773-785
-void Scheduler::applyUsage(NodeEntry& ne, const PodDevices& devs, int sign) {
+void Scheduler::applyUsage(NodeEntry& ne, const PodDevices& devs, int sign, const std::string& appClass) {
   for (auto& kv : devs)
     for (auto& ctrdevs : kv.second)
       for (auto& udevice : ctrdevs)
         for (auto& d : ne.usage)
           if (d.ID == udevice.UUID) {
+            if (appClass == "online") d.OnlinePods += sign;        // d.Device.PodInfos = append(…, p), scheduler.go:786
+            else if (appClass == "offline") d.OfflinePods += sign;
             int32_t slots = std::max(udevice.Slots, 1);
             if (sign > 0) { d.Used = i32add(d.Used, slots); d.Usedmem = i32add(d.Usedmem, udevice.Usedmem); d.Usedcores = i32add(d.Usedcores, udevice.Usedcores); }
             else { d.Used = i32sub(d.Used, slots); d.Usedmem = i32sub(d.Usedmem, udevice.Usedmem); d.Usedcores = i32sub(d.Usedcores, udevice.Usedcores); }
@@ -1770,7 +2003,7 @@ bool Scheduler::DeletePod(const std::string& uid) {
   auto it = pods_.find(uid);
   if (it == pods_.end()) return false;
   auto n = nodeIndex_.find(it->second.NodeID);
-  if (n != nodeIndex_.end()) applyUsage(*nodes_[n->second], it->second.Devices, -1);
+  if (n != nodeIndex_.end()) applyUsage(*nodes_[n->second], it->second.Devices, -1, it->second.AppClass);
   quota.RmUsage(it->second.Namespace, CountPodDevices(it->second.Devices));   // scheduler.go:250-252,1092-1094
   pods_.erase(it);
   if (n != nodeIndex_.end()) refreshMig(*nodes_[n->second]);
@@ -1963,7 +2196,9 @@ NodeScoreResult Scheduler::ScoreNode(const std::string& nodeID, NodeUsage& node,
   for (auto& kv : score.Devices) {
     const Devices* dev = Vendor(kv.first);
     if (!dev) continue;
-    devScore = devScore + dev->ScoreNode(kv.second, userNodePolicy, node.Info, &snapshot);
+    float sc = dev->ScoreNode(kv.second, userNodePolicy, node.Info, &snapshot);
+    if (dev->PolicyNeutralScore()) sc = (userNodePolicy == "spread" ? (float)-10000 : (float)10000) * sc;     // node_policy.go:82-88
+    devScore = devScore + sc;
   }
   score.Score = score.Score + devScore;
   res.fit = true;
@@ -2078,7 +2313,8 @@ FilterResult Scheduler::Filter(const Pod& pod, const std::vector<std::string>* n
   pi.Namespace = pod.Namespace;
   pi.Devices = effective;
   quota.AddUsage(pod.Namespace, CountPodDevices(effective));   // scheduler.go:1136-1138
-  applyUsage(*nodes_[cand[best]], effective, +1);
+  if (auto cls = anno(pod, "metax-tech.com/sgpu-app-class")) pi.AppClass = *cls;
+  applyUsage(*nodes_[cand[best]], effective, +1, pi.AppClass);
   pods_[pod.UID] = pi;      // args.Pod carries no hami.io/vgpu-mig-allocations yet: a MIG pick fails closed until the informer delivers it
   refreshMig(*nodes_[cand[best]]);
   return fr;

@@ -85,6 +85,12 @@ struct DeviceUsage {               // devices.go:106-125
   std::string EnfMinor, EnfIndex;
   std::vector<std::pair<std::string, std::string>> EnfProfiles;
   int EnfMaxSlice = 0;
+  // metax sGPU: CustomInfo["QosPolicy"] / ["LinkZone"] (metax/protocol.go:108-112) and the application classes of the pods
+  // on the device (DeviceUsage.PodInfos, metax/sdevice.go:674-690)
+  bool HasSgpu = false;
+  std::string QosPolicy;
+  int32_t LinkZone = 0;
+  int OnlinePods = 0, OfflinePods = 0;
 };
 
 struct DeviceInfo {                // devices.go:127-144
@@ -103,6 +109,9 @@ struct DeviceInfo {                // devices.go:127-144
   std::string EnfMinor, EnfIndex;         // CustomInfo of an enflame DRS device
   std::vector<std::pair<std::string, std::string>> EnfProfiles;
   int EnfMaxSlice = 0;
+  bool HasSgpu = false;                   // metax sGPU CustomInfo
+  std::string QosPolicy;
+  int32_t LinkZone = 0;
 };
 
 struct NodeInfo {                  // devices.go:170-174 (+ the node annotations Fit reads)
@@ -127,6 +136,12 @@ struct ContainerDevice {           // devices.go:205-216
   bool HasDrs = false;
   std::string DrsProfileName, DrsProfileID, DrsMinor, DrsIndex;
   int DrsSlice = 0, DrsRequestMem = 0, DrsRequestCore = 0;
+  // metax sGPU Fit: CustomInfo = a clone of the device's at Fit time (QosPolicy, LinkZone) + the pod's annotations
+  // (metax/sdevice.go:470-482: "WorkAround" for ScoreNode)
+  bool HasSgpu = false;
+  std::string SgpuQos;
+  int32_t SgpuLinkZone = 0;
+  const std::map<std::string, std::string>* PodAnnotations = nullptr;
 };
 
 struct ContainerDeviceRequest {    // devices.go:222-228
@@ -213,6 +228,10 @@ class Devices {
   // returns false where the reference returns an error (only the NVIDIA MIG branch does, nvidia/device.go:646-650)
   virtual bool AddResourceUsage(DeviceUsage& n, ContainerDevice& ctr) const;
   virtual void PatchAnnotations(const Pod& pod, std::map<std::string, std::string>& annos, const PodDevices& pd) const = 0;
+  // policyNeutralScorer (policy/node_policy.go:55-65): OverrideScore weights the score by +-10000 itself
+  virtual bool PolicyNeutralScore() const { return false; }
+  // GetNodeDevices side effect of the metax sGPU vendor: jqCache.Sync (metax/sdevice.go:131-139, qos.go:37-59)
+  virtual void SyncRegistered(const std::vector<DeviceInfo>&) const {}
 };
 
 struct AscendTemplate { std::string Name; int64_t Memory = 0; };
@@ -228,7 +247,7 @@ struct Config {
   std::vector<AscendConfig> Ascend;
   bool AscendHamiVnpuCore = false;
   // vendors with a plain Fit (hs_vendor_config): iluvatar's CommonWords, biren
-  struct PlainVendor { std::string CommonWord; int FitKind = 0; std::string UseUUID, NoUseUUID, ToAllocate, Allocated, UseType, NoUseType; };
+  struct PlainVendor { std::string CommonWord; int FitKind = 0; std::string UseUUID, NoUseUUID, ToAllocate, Allocated, UseType, NoUseType; int Option = 0; };
   std::vector<PlainVendor> Plain;
 };
 
@@ -236,6 +255,7 @@ struct PodInfo {                   // pkg/device/pods.go:33-40
   std::string NodeID, Namespace;
   PodDevices Devices;              // collapsed
   std::vector<MigReservation> MigAllocs;   // DecodeMigAllocations(pod.Annotations["hami.io/vgpu-mig-allocations"]), in order
+  std::string AppClass;                    // pod.Annotations["metax-tech.com/sgpu-app-class"]: read through DeviceUsage.PodInfos
 };
 
 struct FilterResult {
@@ -301,7 +321,7 @@ class Scheduler {
     bool alive = true;
     bool migTouched = false;         // refreshMig changed Health / reservations last time: the next call must reset them
   };
-  void applyUsage(NodeEntry& ne, const PodDevices& devs, int sign);
+  void applyUsage(NodeEntry& ne, const PodDevices& devs, int sign, const std::string& appClass = std::string());
   void refreshMig(NodeEntry& ne);   // the MIG half of getNodesUsage (scheduler.go:757-842) for one node
   void scoreRange(const std::vector<int>& cand, size_t lo, size_t hi, const Pod& pod,
                   const std::string& userNodePolicy, const DeviceScoringWeights& w,

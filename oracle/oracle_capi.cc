@@ -19,7 +19,8 @@ static const char* kReasonNames[HS_R_COUNT] = {
     "CardTypeMismatch", "CardUuidMismatch", "CardTimeSlicingExhausted", "CardComputeUnitsExhausted",
     "CardInsufficientMemory", "CardInsufficientCore", "CardNotHealth", "CardCordoned", "NumaNotFit",
     "ExclusiveDeviceAllocateConflict", "CardNotFoundCustomFilterRule", "CardMigTopologyInfeasible",
-    "AllocatedCardsInsufficientRequest", "ResourceQuotaNotFit", "ModeNotFit"};
+    "AllocatedCardsInsufficientRequest", "ResourceQuotaNotFit", "ModeNotFit",
+    "CardUnhealthy", "CardAppClassMismatch", "CardQosPolicyMismatch"};
 
 struct Arena {
   std::deque<std::string> strs;
@@ -79,6 +80,7 @@ NodeInfo toNodeInfo(const hs_node_info* n) {
     di.DeviceVendor = str(d.vendor);
     di.HasNetworkID = d.network_id >= 0; di.NetworkID = d.network_id >= 0 ? d.network_id : 0;
     di.MIGProfiles = toMigProfiles(d.mig_profiles, d.n_mig_profiles);
+    if (d.sgpu) { di.HasSgpu = true; di.QosPolicy = str(d.sgpu->qos_policy); di.LinkZone = d.sgpu->link_zone; }
     if (d.enflame) {
       di.EnfMinor = str(d.enflame->minor); di.EnfIndex = str(d.enflame->index); di.EnfMaxSlice = d.enflame->max_slice;
       for (uint32_t k = 0; k < d.enflame->n_profiles; k++) di.EnfProfiles.emplace_back(str(d.enflame->profiles[k].key), str(d.enflame->profiles[k].value));
@@ -103,6 +105,8 @@ DeviceListsScore toDls(const oracle_dev& d) {
   ds.Device.Health = d.health != 0; ds.Device.HasNetworkID = d.network_id >= 0;
   ds.Device.NetworkID = d.network_id >= 0 ? d.network_id : 0;
   ds.Device.MigProfiles = toMigProfiles(d.mig_profiles, d.n_mig_profiles);
+  if (d.sgpu) { ds.Device.HasSgpu = true; ds.Device.QosPolicy = str(d.sgpu->qos_policy); ds.Device.LinkZone = d.sgpu->link_zone; }
+  ds.Device.OnlinePods = d.online_pods; ds.Device.OfflinePods = d.offline_pods;
   if (d.enflame) {
     ds.Device.EnfMinor = str(d.enflame->minor); ds.Device.EnfIndex = str(d.enflame->index); ds.Device.EnfMaxSlice = d.enflame->max_slice;
     for (uint32_t k = 0; k < d.enflame->n_profiles; k++) ds.Device.EnfProfiles.emplace_back(str(d.enflame->profiles[k].key), str(d.enflame->profiles[k].value));
@@ -171,6 +175,7 @@ oracle_handle* oracle_create(const hs_config* cfg) {
       pv.NoUseUUID = v.nouse_uuid_key ? v.nouse_uuid_key : "hami.io/no-use-" + pv.CommonWord + "-uuid";
       pv.ToAllocate = v.to_allocate_key ? v.to_allocate_key : "hami.io/" + pv.CommonWord + "-devices-to-allocate";
       pv.Allocated = v.allocated_key ? v.allocated_key : "hami.io/" + pv.CommonWord + "-devices-allocated";
+      pv.Option = v.option;
       pv.UseType = str(v.use_type_key);
       pv.NoUseType = str(v.nouse_type_key);
       c.Plain.push_back(pv);
@@ -243,6 +248,26 @@ int32_t oracle_mig_select_candidate(const hs_mig_profile* profiles, uint32_t n, 
   if (profile_index) { *profile_index = -1; for (uint32_t i = 0; i < n; i++) if (ps[i].Name == pr.Name) { *profile_index = (int32_t)i; break; } }
   if (out) { out->start = pl.Start; out->size = pl.Size; }
   return 1;
+}
+// MetaxSDevices.ScoreNode (metax/sdevice.go:295-304) on explicit picks: zones[i] = CustomInfo["LinkZone"] of pick i (NULL: no
+// CustomInfo), annos = the pod's annotations riding in CustomInfo["Pod.Annotations"], prev = `previous`
+float oracle_sgpu_score(oracle_handle* o, const hs_alloc_entry* picks, uint32_t n_picks, const int32_t* zones,
+                        const oracle_dev* prev, uint32_t n_prev, const hs_kv* annos, uint32_t n_annos) {
+  const Devices* v = o->s->Vendor("Metax-SGPU");
+  if (!v) return -1e30f;
+  std::map<std::string, std::string> pa;
+  for (uint32_t i = 0; i < n_annos; i++) pa[str(annos[i].key)] = str(annos[i].value);
+  PodSingleDevice psd;
+  for (uint32_t i = 0; i < n_picks; i++) {
+    while (psd.size() <= picks[i].container) psd.push_back({});
+    ContainerDevice cd;
+    cd.UUID = str(picks[i].uuid); cd.Usedcores = picks[i].usedcores; cd.Usedmem = picks[i].usedmem;
+    cd.HasSgpu = zones != nullptr; cd.SgpuLinkZone = zones ? zones[i] : 0; cd.PodAnnotations = &pa;
+    psd[picks[i].container].push_back(cd);
+  }
+  std::vector<DeviceUsage> previous;
+  for (uint32_t i = 0; i < n_prev; i++) previous.push_back(toDls(prev[i]).Device);
+  return v->ScoreNode(psd, "", nullptr, &previous);
 }
 float oracle_kunlun_calc_score(const int32_t* prev, uint32_t n_prev, const int32_t* cur, uint32_t n_cur) {
   auto dedup = [](const int32_t* v, uint32_t n) {       // addidx, kunlun/topo.go:40-48

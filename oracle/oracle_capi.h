@@ -32,6 +32,8 @@ typedef struct oracle_dev {
   const hs_mig_placement* mig_in_use;     /* placements of DeviceUsage.MigAllocationsInUse */
   uint32_t                n_mig_in_use;
   const hs_enflame_info*  enflame;        /* CustomInfo of an enflame DRS device */
+  const hs_metax_sgpu_info* sgpu;         /* CustomInfo of a metax sGPU device */
+  int32_t                 online_pods, offline_pods;   /* DeviceUsage.PodInfos by metax-tech.com/sgpu-app-class */
 } oracle_dev;
 
 oracle_handle* oracle_create(const hs_config* cfg);
@@ -44,6 +46,9 @@ int32_t oracle_usage_apply(oracle_handle* o, const char* pod_uid, const char* no
                            int32_t slots, int32_t usedmem, int32_t usedcores);
 int32_t oracle_pod_delete(oracle_handle* o, const char* pod_uid);
 /* calcscore (kunlun/topo.go:74-95) after addidx's dedup */
+/* MetaxSDevices.ScoreNode (metax/sdevice.go:295-304) before OverrideScore's +-10000 weight */
+float   oracle_sgpu_score(oracle_handle* o, const hs_alloc_entry* picks, uint32_t n_picks, const int32_t* zones,
+                          const oracle_dev* prev, uint32_t n_prev, const hs_kv* annos, uint32_t n_annos);
 float   oracle_kunlun_calc_score(const int32_t* prev, uint32_t n_prev, const int32_t* cur, uint32_t n_cur);
 /* dynamic MIG: the informer side and the state getNodesUsage derives (see hs_pod_set_mig / hs_snapshot_node_mig) */
 int32_t oracle_pod_set_mig(oracle_handle* o, const char* pod_uid, const hs_mig_reservation* res, uint32_t n);

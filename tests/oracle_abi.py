@@ -21,7 +21,8 @@ class oracle_dev(C.Structure):
                 ("network_id", C.c_int32), ("score", C.c_float),
                 ("mig_profiles", C.POINTER(abi.hs_mig_profile)), ("n_mig_profiles", C.c_uint32),
                 ("mig_in_use", C.POINTER(abi.hs_mig_placement)), ("n_mig_in_use", C.c_uint32),
-                ("enflame", C.POINTER(abi.hs_enflame_info))]
+                ("enflame", C.POINTER(abi.hs_enflame_info)), ("sgpu", C.POINTER(abi.hs_metax_sgpu_info)),
+                ("online_pods", C.c_int32), ("offline_pods", C.c_int32)]
 
 
 _lib = None
@@ -102,6 +103,25 @@ def placements_array(pl):
     return arr
 
 
+def sgpu_from_go(ci):
+    """Go CustomInfo of a metax sGPU device ({"QosPolicy", "LinkZone"}) -> hs_metax_sgpu_info*"""
+    if not isinstance(ci, dict) or not ("QosPolicy" in ci or "LinkZone" in ci):
+        return None
+    return abi.build_sgpu_info({"qos_policy": ci.get("QosPolicy", ""), "link_zone": int(ci.get("LinkZone", 0))}, _mig_keep)
+
+
+def pod_classes_from_go(d):
+    """DeviceUsage.PodInfos -> (pods with metax-tech.com/sgpu-app-class online, … offline)"""
+    on = off = 0
+    for pi in d.get("PodInfos") or []:
+        pod = pi.get("Pod") if isinstance(pi, dict) else None
+        annos = (((pod or {}).get("ObjectMeta") or {}).get("Annotations")) or {}
+        cls = annos.get("metax-tech.com/sgpu-app-class")
+        on += cls == "online"
+        off += cls == "offline"
+    return on, off
+
+
 def enflame_from_go(ci):
     """Go CustomInfo of an enflame DRS device ({"minor","index","profiles": {name: id},"maxSlice"}) -> hs_enflame_info*"""
     if not isinstance(ci, dict) or "profiles" not in ci:
@@ -128,7 +148,7 @@ def dev_from_go(d, score=0.0):
                       int(d.get("Usedmem", 0)), int(d.get("Totalmem", 0)), int(d.get("Totalcore", 0)),
                       int(d.get("Usedcores", 0)), abi._b(d.get("Mode", "")), int(d.get("Numa", 0)),
                       abi._b(d.get("Type", "")), 1 if d.get("Health", False) else 0, net, float(score),
-                      mp, nmp, iu, len(inuse), enflame_from_go(ci))
+                      mp, nmp, iu, len(inuse), enflame_from_go(ci), sgpu_from_go(ci), *pod_classes_from_go(d))
 
 
 def devs_array(devs):

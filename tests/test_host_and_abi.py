@@ -46,7 +46,7 @@ def test_struct_sizes_match_header():
     assert C.sizeof(abi.hs_container_request) == 32
     assert C.sizeof(abi.hs_alloc_entry) == 56      # + mig_profile / mig_start / mig_size
     assert C.sizeof(abi.hs_mig_profile) == 40 and C.sizeof(abi.hs_mig_placement) == 8
-    assert C.sizeof(abi.hs_device_info) == 96 and C.sizeof(abi.hs_container) == 24 and C.sizeof(abi.hs_enflame_info) == 40
+    assert C.sizeof(abi.hs_device_info) == 104 and C.sizeof(abi.hs_container) == 24 and C.sizeof(abi.hs_enflame_info) == 40
     assert C.sizeof(abi.hs_kv) == 16
     assert C.sizeof(abi.hs_device_usage_row) == 12
 

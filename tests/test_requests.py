@@ -226,7 +226,7 @@ def product_generate(vendors, limits, requests):
     def arr(d):
         a = (abi.hs_quantity * max(len(d), 1))()
         for i, (k, q) in enumerate(d.items()):
-            a[i] = abi.hs_quantity(abi._b(k), q[0], 1 if q[1] else 0, q[2], q[3])
+            a[i] = abi.hs_quantity(abi._b(k), q[0], 1 if q[1] else 0, q[2], q[3], 1 if len(q) > 4 and q[4] else 0)
         return a
     la, ra = arr(limits), arr(requests)
     ctr = abi.hs_container_resources(la, len(limits), ra, len(requests))

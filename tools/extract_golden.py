@@ -338,6 +338,10 @@ IDENTS = {
     "EnflameGCUDevice": "GCU", "KunlunGPUDevice": "kunlun", "KunlunGPUCommonWord": "kunlun", "kunlun.KunlunGPUDevice": "kunlun",
     "XPUDevice": "XPU", "KunlunResourceVCount": "kunlunxin.com/vxpu", "KunlunResourceVMemory": "kunlunxin.com/vxpu-memory",
     "KunlunMaxMemory": 98304,
+    "MetaxSGPUDevice": "Metax-SGPU", "MetaxSGPUCommonWord": "Metax-SGPU", "MetaxSGPUAppClass": "metax-tech.com/sgpu-app-class",
+    "MetaxSGPUQosPolicy": "metax-tech.com/sgpu-qos-policy", "MetaxSGPUTopologyAware": "metax-tech.com/sgpu-topology-aware",
+    "Online": "online", "Offline": "offline", "BestEffort": "best-effort", "FixedShare": "fixed-share", "BurstShare": "burst-share",
+    "MetaxUseUUID": "metax-tech.com/use-gpuuuid", "MetaxNoUseUUID": "metax-tech.com/nouse-gpuuuid",
     "BirenDevice": "Biren", "BirenCommonWord": "Biren",
     "BirenUseUUID": "birentech.com/use-gpuuuid", "BirenNoUseUUID": "birentech.com/nouse-gpuuuid",
 }
@@ -404,7 +408,10 @@ def find_func(src, name):
 
 
 def extract_table(body, var="tests"):
-    m = re.search(r"\b%s\s*:?=\s*(\[\]struct\s*\{)" % var, body)
+    if var is None:      # `for _, ts := range []struct{…}{…}`: the table literal sits in the range clause
+        m = re.search(r"\brange\s+(\[\]struct\s*\{)", body)
+    else:
+        m = re.search(r"\b%s\s*:?=\s*(\[\]struct\s*\{)" % var, body)
     if not m:
         raise KeyError("no table %s" % var)
     toks = tokenize(body[m.start(1):])
@@ -473,6 +480,15 @@ TABLES = [
     ("kunlun_graph_select_vxpu", "pkg/device/kunlun/device_test.go", "Test_graphSelectVXPU", "tests"),
     ("kunlun_vxpu_generate_requests", "pkg/device/kunlun/vdevice_test.go", "Test_KunlunVDevices_GenerateResourceRequests", "tests"),
     ("kunlun_fit_vxpu_direct", "pkg/device/kunlun/vdevice_test.go", "Test_FitVXPU_direct", "tests"),
+    # metax sGPU ("Metax-SGPU"): filter-then-prioritise, application classes, QoS, MetaLink scores
+    ("metax_sgpu_fit", "pkg/device/metax/sdevice_test.go", "TestMetaxSDevices_Fit", "tests"),
+    ("metax_sgpu_generate_requests", "pkg/device/metax/sdevice_test.go", "TestGenerateResourceRequests", None),
+    ("metax_sgpu_check_qos", "pkg/device/metax/sdevice_test.go", "TestCheckDeviceQos", None),
+    ("metax_sgpu_prioritize_exclusive", "pkg/device/metax/sdevice_test.go", "TestPrioritizeExclusiveDevices", None),
+    ("metax_sgpu_score_exclusive", "pkg/device/metax/sdevice_test.go", "TestScoreExclusiveDevices", None),
+    ("metax_sgpu_check_app_class", "pkg/device/metax/sdevice_test.go", "TestCheckAppClass", None),
+    ("metax_sgpu_prioritize_online", "pkg/device/metax/sdevice_test.go", "TestPrioritizeOnlineDevices", None),
+    ("metax_sgpu_score_online", "pkg/device/metax/sdevice_test.go", "TestScoreOnlineDevices", None),
 ]
 
 
