@@ -618,6 +618,10 @@ int32_t hs_decode_mig_allocations(const char* json, const hs_mig_reservation** o
  * is covered by a reservation in use) and whether the device is healthy after the fail-closed rules.  Rows in the
  * node's device order; returns the number of devices.                                                           */
 int32_t hs_snapshot_node_mig(hs_handle* h, const char* node, uint32_t* occupied, uint8_t* health, uint32_t cap);
+/* The metax sGPU bookkeeping of one node, per device in the node's device order: the online / offline pods on it
+ * (DeviceUsage.PodInfos by metax-tech.com/sgpu-app-class) and the QoS policy a previous Filter is switching it to
+ * (JitteryQosCache; NULL = none; the strings belong to the handle).  Returns the number of devices.                 */
+int32_t hs_snapshot_node_sgpu(hs_handle* h, const char* node, int32_t* online, int32_t* offline, const char** pending, uint32_t cap);
 
 /* ---- namespace quota: device.QuotaManager, pkg/device/quota.go ------------------------------
  * The NVIDIA and MLU Fit refuse a device when the pod's collapsed total would push the namespace past a configured
@@ -684,6 +688,9 @@ int32_t hs_sweep_static(hs_handle* h, const hs_pod* pod, void* out_device16, voi
  * whole inventory (no commit); average device ms per sweep, the winning candidate position, its score. */
 int32_t hs_sweep_probe(hs_handle* h, const hs_pod* pod, uint32_t iters, double* ms_avg, int32_t* node_index, float* score);
 /* When each Filter decision of the last hs_run_batch became final on the device (%globaltimer ns; 0 = not a Filter). */
+/* test hook: the dynamic records of one node as the DEVICE holds them ({used, usedmem, usedcores, dflags} x 8) next to the
+ * host mirror's — after a batch the two must be identical (the kernel's commits / releases and the host's replay of them). */
+int32_t hs_debug_device_rows(hs_handle* h, const char* node, int32_t device_rows[32], int32_t mirror_rows[32]);
 int32_t hs_debug_decision_ns(hs_handle* h, uint64_t* out, uint32_t cap);
 /* Cumulative SM clocks block 0 spent per phase of the decide loop (needs HS_TIMING=1 at hs_create). */
 int32_t hs_debug_timing(hs_handle* h, unsigned long long out[8]);

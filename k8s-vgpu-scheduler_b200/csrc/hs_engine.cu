@@ -67,6 +67,11 @@ std::string lower(std::string s) { for (auto& c : s) if (c >= 'A' && c <= 'Z') c
 bool parseBoolTrue(const std::string& s) {  // strconv.ParseBool(s) == (true, nil)
   return s == "1" || s == "t" || s == "T" || s == "TRUE" || s == "true" || s == "True";
 }
+bool parseBool(const std::string& s, bool& v) {  // strconv.ParseBool
+  if (parseBoolTrue(s)) { v = true; return true; }
+  if (s == "0" || s == "f" || s == "F" || s == "FALSE" || s == "false" || s == "False") { v = false; return true; }
+  return false;
+}
 bool policyContains(const std::string& policy, const char* name) {  // util/util.go:290-298
   for (auto& p : splitComma(policy)) if (trimSpace(p) == name) return true;
   return false;
@@ -125,6 +130,7 @@ struct DevSlot {
   int32_t count = 0, devmem = 0, devcore = 0, numa = 0, network_id = -1;
   bool health = true;
   int type_id = 0, mode_id = 0, vendor_id = 0;
+  bool sgpu = false;        // a metax sGPU device (DF_SGPU)
   int mig_geom = 0;         // index into hs_handle::mig_geoms for a GPU in MIG mode (0 = the empty geometry); enflame: the node's profile table
   std::string enf_minor, enf_index;                               // enflame CustomInfo["minor"] / ["index"]
   std::vector<std::pair<std::string, std::string>> enf_profiles;  // … ["profiles"]
@@ -171,6 +177,8 @@ struct VendorInfo {
   bool metax = false;       // metax whole GPUs: mthreads' gates without uuid lists + ScoreNode from the node's annotations (EF_METAX)
   int fit_kind = 0;         // HS_FIT_* as registered (hs_filter_simulate hands it on to the child handle)
   bool vastai = false;      // vastai: count-only gates + die mode (EF_VASTAI)
+  bool sgpu = false;        // metax sGPU: application classes, QoS switches, MetaLink prioritisation, policy-neutral ScoreNode (EF_SGPU)
+  int option = 0;           // hs_vendor_config.option (sGPU: MetaxConfig.TopologyAware)
   bool enflame = false;     // enflame shared vGCU: DRS profile selection per request (EF_ENFLAME)
   bool kunlun = false;      // kunlun whole XPUs: graghSelect, slot-only usage, wing ScoreNode (EF_KUNLUN)
   bool vxpu = false;        // … the shared "XPU" type on the same graghSelect (EF_KUNLUN | EF_VXPU)
@@ -186,6 +194,7 @@ struct PodRec {           // podManager entry: what to subtract when the pod goe
   std::vector<std::pair<std::string, int4>> parked;   // usage on devices that left the node's register annotation, by UUID
   uint8_t n_ent[HS_D] = {0, 0, 0, 0, 0, 0, 0, 0};     // cached ContainerDevice entries per device slot (getNodesUsage visits each one)
   std::vector<MigRes> mig;                            // decoded hami.io/vgpu-mig-allocations, annotation order
+  uint8_t app_class = 0;                              // metax-tech.com/sgpu-app-class of the pod: 1 online, 2 offline (DeviceUsage.PodInfos)
 };
 
 struct EntryMeta {
@@ -198,6 +207,7 @@ struct OpMeta {           // host-side memory of one op of the current batch
   int kind = OP_NOP;      // OP_FILTER / OP_RELEASE / OP_NOP
   int status = HS_OK;     // compile-time verdict: HS_PASSTHROUGH / HS_ERR_*
   std::string uid, vnpu_mode, ns;
+  int sg_class = 0, sg_qos = 0;         // metax sGPU: the pod's application class (0 none, 1 online, 2 offline, 3 other) and QoS id
   std::vector<std::string> ctr_names;   // Container.Name by position (enflame's assigned-containers annotation)
   int n_ctr = 0, n_init = 0;
   std::vector<EntryMeta> entries;
@@ -694,6 +704,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
   }
   std::string vgpuMode;
   bool hasVgpuMode = get_anno(pod, "nvidia.com/vgpu-mode", vgpuMode);
+  bool has_sgpu = false, sgpu_topo_default = false;
 
   p.n_ctr = (uint8_t)pod->n_containers;
   p.n_init = (uint8_t)c.meta.n_init;
@@ -728,6 +739,11 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
       if (v && v->whole_card) e.flags |= EF_WHOLE_CARD;
       if (v && v->kunlun) e.flags |= EF_KUNLUN;
       if (v && v->enflame) e.flags |= EF_ENFLAME;
+      if (v && v->sgpu) {
+        e.flags |= EF_SGPU;
+        sgpu_topo_default = v->option != 0;
+        has_sgpu = true;
+      }
       if (v && v->vxpu) e.flags |= EF_VXPU;
       auto masks = entry_masks(h, v, ktype, pod);
       e.type_contains = masks[0]; e.type_equal = masks[1]; e.type_allow = masks[2]; e.mode_allow = (uint32_t)masks[3];
@@ -771,7 +787,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
           if (!uuid_words(h, list, uuid_pool, e.nouse_off, e.nouse_cnt)) { h->err = "no-use-uuid list spans too many nodes"; return HS_ERR_UNSUPPORTED; }
       }
       keyset.insert(ktype);
-      if (v && (v->ascend910 || v->metax || v->vastai)) slotset.insert(ktype);   // vendors whose ScoreNode is not constant 0
+      if (v && (v->ascend910 || v->metax || v->vastai || v->sgpu)) slotset.insert(ktype);   // vendors whose ScoreNode is not constant 0
       c.entries.push_back(e);
       c.meta.entries.push_back(EntryMeta{ktype, (int)ci, v ? v->id : -1});
       int nn = q->nums < 0 ? 0 : (q->nums > HS_D ? HS_D : q->nums);
@@ -789,6 +805,21 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     auto s = slotset.find(t);
     if (s != slotset.end()) c.entries[i].score_slot = (int8_t)std::distance(slotset.begin(), s);
   }
+  if (has_sgpu) {       // metax sGPU reads three pod annotations (metax/protocol.go:33-37)
+    std::string v;
+    int cls = 0;
+    if (get_anno(pod, "metax-tech.com/sgpu-app-class", v)) cls = v == "online" ? 1 : (v == "offline" ? 2 : 3);
+    bool topo = sgpu_topo_default;
+    if (get_anno(pod, "metax-tech.com/sgpu-topology-aware", v)) { bool b; if (parseBool(v, b)) topo = b; }
+    p.sg_class = (uint8_t)(cls | (topo ? 4 : 0));
+    int q = 0;
+    if (get_anno(pod, "metax-tech.com/sgpu-qos-policy", v)) {
+      q = 7;                                     // a value no device can carry …
+      for (size_t i = 0; i < h->modes.size() && i < 7; i++) if (h->modes[i] == v) q = (int)i;   // … unless the table holds it
+    }
+    p.sg_qos = (uint8_t)q;
+    c.meta.sg_class = cls; c.meta.sg_qos = q;
+  }
   if (!c.entries.empty()) {
     p.e0 = c.entries[0];
     const DevEntry& e = c.entries[0];
@@ -796,7 +827,7 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
     // pairing stays with the general evaluator
     p.fast = (c.entries.size() == 1 && c.meta.n_init == 0 && e.nums >= 1 && e.nums <= HS_D && e.vendor != HV_NONE &&
               !(e.flags & EF_ASCEND910C)) ? 1 : 0;
-    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX | EF_NEURON | EF_KUNLUN | EF_ENFLAME))) p.fast = 0;
+    if (h->no_fast || (e.flags & (EF_COUNT_ONLY | EF_AMD | EF_MTHREADS | EF_WHOLE_CARD | EF_METAX | EF_NEURON | EF_KUNLUN | EF_ENFLAME | EF_SGPU))) p.fast = 0;
   }
   if (h->has_mig)       // dynamic MIG lives in the general evaluator: every NVIDIA request of a handle that holds a GPU in MIG mode
     for (const DevEntry& e : c.entries) {
@@ -1078,6 +1109,20 @@ void mig_apply_orphan(hs_handle* h, int slot, const PodRec& pr, int sign) {
   }
 }
 
+// metax sGPU: a pod of class `cls` (1 online, 2 offline) joins (+1) or leaves (-1) the PodInfos of the sGPU devices it has
+// entries on — once per cached entry (scheduler.go:786)
+void sgpu_apply_class(hs_handle* h, int slot, const uint8_t* n_ent, int cls, int sign) {
+  if (cls != 1 && cls != 2) return;
+  const int sh = cls == 1 ? 16 : 22;
+  for (int d = 0; d < HS_D; d++) {
+    int4& v = h->h_dyn[inv_idx(slot, d)];
+    if (!((uint32_t)v.w & DF_SGPU) || n_ent[d] == 0) continue;
+    int c = (int)(((uint32_t)v.w >> sh) & 63u) + sign * (int)n_ent[d];
+    c = c < 0 ? 0 : (c > 63 ? 63 : c);
+    v.w = (int)(((uint32_t)v.w & ~(63u << sh)) | ((uint32_t)c << sh));
+  }
+}
+
 // Bring the node's dflags (host mirror) in line with the pod cache; true when something changed.
 bool mig_refresh(hs_handle* h, int slot) {
   NodeSlot& ns = h->nodes[slot];
@@ -1088,6 +1133,7 @@ bool mig_refresh(hs_handle* h, int slot) {
   bool changed = false;
   for (int d = 0; d < HS_D; d++) {
     int4& v = h->h_dyn[inv_idx(slot, d)];
+    if ((uint32_t)v.w & DF_SGPU) continue;       // a metax sGPU device keeps its own bookkeeping in those bits
     const uint32_t nf = mig_dflags((uint32_t)v.w, occ[d], bad[d]);
     if (nf != (uint32_t)v.w) { v.w = (int)nf; changed = true; }
   }
@@ -1617,6 +1663,28 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
         }
         continue;
       }
+      if (v.sgpu) {
+        // metax/sdevice.go:142-171: both hami keys, the pod's devices in metax's own JSON (protocol.go:118-134; compute and
+        // vRam omitted when 0), the (blanked) predicate time
+        annos[v.to_allocate] = s;
+        annos[v.allocated] = s;
+        std::string js = "[";
+        for (size_t c = 0; c < it->second.size(); c++) {
+          js += c ? ",[" : "[";
+          for (size_t d = 0; d < it->second[c].size(); d++) {
+            const hs_alloc_entry* e = it->second[c][d];
+            js += d ? ",{" : "{";
+            js += "\"uuid\":" + json_string(e->uuid);
+            if (e->usedcores != 0) js += ",\"compute\":" + std::to_string(e->usedcores);
+            if (e->usedmem != 0) js += ",\"vRam\":" + std::to_string(e->usedmem);
+            js += "}";
+          }
+          js += "]";
+        }
+        annos["metax-tech.com/gpu-devices-allocated"] = js + "]";
+        annos["metax-tech.com/predicate-time"] = "";
+        continue;
+      }
       if (v.enflame) {
         // enflame/device.go:254-300: the allocated key, gcu-assigned, the (blanked) time, the first container's index /
         // minor / slice count and assigned-containers keyed by container name
@@ -1735,13 +1803,13 @@ void assemble_result(hs_handle* h, int op, hs_filter_result* out) {
         for (size_t s = 0; s < nn; s++) if (h->h_flags[s] & NF_ALIVE) h->r_failed[k++] = hs_failed_node{h->name_ptr[s], ""};
       } else {
         const char* last = nullptr;
-        uint32_t l0 = 0xffffffffu, l1 = 0, l2 = 0;
+        uint32_t l0 = 0xffffffffu, l1 = 0, l2 = 0, l3 = 0;
         for (size_t s = 0; s < nn; s++) {
           if (!(h->h_flags[s] & NF_ALIVE)) continue;
           const DevFail& f = fr[s];
-          if (!last || f.kind_cards != l0 || f.c0 != l1 || f.c1 != l2) {
+          if (!last || f.kind_cards != l0 || f.c0 != l1 || f.c1 != l2 || f.pad != l3) {
             last = fail_string(h, f).c_str();
-            l0 = f.kind_cards; l1 = f.c0; l2 = f.c1;
+            l0 = f.kind_cards; l1 = f.c0; l2 = f.c1; l3 = f.pad;
           }
           h->r_failed[k++] = hs_failed_node{h->name_ptr[s], last};
         }
@@ -1791,7 +1859,11 @@ bool stage_release(hs_handle* h, const std::string& uid, std::unordered_map<std:
     p.rel_node = it->second.node;
     p.rel_off = (int32_t)rel.size();
     for (int d = 0; d < HS_D; d++) { int4 v = it->second.delta[d]; v.w = 0; rel.push_back(v); }
-    if (h->nodes[it->second.node].has_mig || !it->second.mig.empty()) {
+    if (it->second.app_class) {          // metax sGPU: the pod leaves the PodInfos of its devices (rows .w bits 2-3 = its class)
+      for (int d = 0; d < HS_D; d++)
+        if (it->second.n_ent[d] && ((uint32_t)h->h_dyn[inv_idx(it->second.node, d)].w & DF_SGPU)) rel[(size_t)p.rel_off + d].w = (int)it->second.app_class << 2;
+      p.flags |= PF_REL_MIG;
+    } else if (h->nodes[it->second.node].has_mig || !it->second.mig.empty()) {
       // MIG bookkeeping of the release (PF_REL_MIG): whether this pod was one of those that make a device fail closed,
       // and the slices still covered by the reservations of the pods that remain (pods released earlier in this
       // batch are gone; pods committed in this batch carry no reservation yet)
@@ -1847,6 +1919,18 @@ void absorb_results(hs_handle* h, int first, int last) {
       apply_host_delta(h, dec.node, pr.delta, +1);
       pr.ns = m.ns;
       quota_track(h, m.ns, dec.node, pr.delta, +1);
+      if (m.sg_class == 1 || m.sg_class == 2) {            // metax sGPU: the pod joins its devices' PodInfos with its class
+        pr.app_class = (uint8_t)m.sg_class;
+        sgpu_apply_class(h, dec.node, pr.n_ent, m.sg_class, +1);
+      }
+      if (m.sg_class != 1)                                  // … and addJitteryQos leaves a QoS switch in flight (metax/sdevice.go:558-581)
+        for (uint32_t i = 0; i < dec.n_alloc; i++) {
+          const DevAlloc& a = h->b_alloc.h[dec.alloc_off + i];
+          int4& v = h->h_dyn[inv_idx(dec.node, AL_DEV(a))];
+          if (!((uint32_t)v.w & DF_SGPU) || !AL_MIG(a)) continue;
+          const uint32_t expected = a.usedcores == 100 ? 0u : ((uint32_t)m.sg_qos & 7u);
+          if ((uint32_t)AL_MIG_CAND(a) != expected) v.w = (int)(((uint32_t)v.w & 0x0fffffffu) | (1u << 28) | (expected << 29));
+        }
       h->pods[m.uid] = pr;
       if (h->nodes[dec.node].has_mig) mig_apply_orphan(h, dec.node, pr, +1);
     } else if (m.kind == OP_RELEASE) {
@@ -1856,6 +1940,8 @@ void absorb_results(hs_handle* h, int first, int last) {
         quota_track(h, m.ns, p.rel_node, h->b_rel.h + p.rel_off, -1);
         auto known = h->pods.find(m.uid);  // podManager.DelPod: only now, with the device's release done
         bool full = (p.flags & PF_REL_MIG) != 0;
+        if (known != h->pods.end() && known->second.app_class) sgpu_apply_class(h, p.rel_node, known->second.n_ent, known->second.app_class, -1);
+        if (full && !h->nodes[p.rel_node].has_mig && (known == h->pods.end() || known->second.mig.empty())) full = false;   // class counts only
         if (known != h->pods.end()) {
           h->n_parked -= known->second.parked.size();
           if (!known->second.mig.empty()) h->n_mig_pods--;
@@ -1870,6 +1956,7 @@ void absorb_results(hs_handle* h, int first, int last) {
           quota_track(h, it->second.ns, it->second.node, it->second.delta, -1);
           h->n_parked -= it->second.parked.size();
           const int rel_node = it->second.node;
+          if (it->second.app_class) sgpu_apply_class(h, rel_node, it->second.n_ent, it->second.app_class, -1);
           if (h->nodes[rel_node].has_mig) mig_apply_orphan(h, rel_node, it->second, -1);   // committed in this batch: no reservation yet
           h->pods.erase(it);
         }
@@ -2409,6 +2496,8 @@ hs_handle* hs_create(const hs_config* cfg) {
       v.metax = vc.fit_kind == HS_FIT_METAX;
       v.neuron = vc.fit_kind == HS_FIT_NEURON;
       v.enflame = vc.fit_kind == HS_FIT_ENFLAME_VGCU;
+      v.sgpu = vc.fit_kind == HS_FIT_METAX_SGPU;
+      v.option = vc.option;
       v.kunlun = vc.fit_kind == HS_FIT_KUNLUN || vc.fit_kind == HS_FIT_KUNLUN_VXPU;
       v.vxpu = vc.fit_kind == HS_FIT_KUNLUN_VXPU;
       if (v.metax) { v.use_uuid.clear(); v.nouse_uuid.clear(); }   // checkUUID is constant true (metax/device.go:124-126)
@@ -2420,6 +2509,8 @@ hs_handle* hs_create(const hs_config* cfg) {
       if (vc.allocated_key) v.allocated = vc.allocated_key;
     }
   h->modes = {"", "hami-core", "mig", "mps"};
+  for (const auto& v : h->vendors)       // metax sGPU: the three QoS policies share the mode table (ids 4-6), so a pod's policy and a device's compare by id
+    if (v.sgpu) { h->modes.push_back("best-effort"); h->modes.push_back("fixed-share"); h->modes.push_back("burst-share"); break; }
   const char* blk = getenv("HS_BLOCK");
   if (blk) { int b = atoi(blk); if (b >= 32 && b <= 512 && b % 32 == 0) h->block = b; }
   h->no_fast = getenv("HS_NO_FAST") != nullptr;
@@ -2510,6 +2601,17 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
     }
     if (s.vendor_id != HV_NONE && h->vendors[s.vendor_id].neuron && (s.devcore > 32767 || s.devcore < 0)) {
       h->err = "AWS Neuron core mask outside the engine's int16 allocation row"; return HS_ERR_UNSUPPORTED;
+    }
+    if (s.vendor_id != HV_NONE && h->vendors[s.vendor_id].sgpu) {
+      // metax sGPU: the registered QoS policy rides in the mode bits, the MetaLink zone in the NetworkID byte
+      if (h->shard_world > 1) { h->err = "metax sGPU nodes are not supported on the sharded (multi-GPU) path"; return HS_ERR_UNSUPPORTED; }
+      s.sgpu = true;
+      s.mode = d.sgpu && d.sgpu->qos_policy ? d.sgpu->qos_policy : "";
+      s.network_id = d.sgpu ? d.sgpu->link_zone : 0;
+      if (s.network_id < 0 || s.network_id > 254) { h->err = "metax sGPU LinkZone outside 0..254"; return HS_ERR_UNSUPPORTED; }
+      if (s.count > 63) { h->err = "metax sGPU device with more than 63 slots (the per-device pod class counters are 6 bits)"; return HS_ERR_UNSUPPORTED; }
+      s.mode_id = intern_mode(h, s.mode);
+      if (s.mode_id < 0 || s.mode_id > 6) { h->err = "more distinct device modes / QoS policies than supported"; return HS_ERR_UNSUPPORTED; }
     }
     if (d.enflame) {
       s.enf_minor = d.enflame->minor ? d.enflame->minor : ""; s.enf_index = d.enflame->index ? d.enflame->index : "";
@@ -2638,6 +2740,16 @@ int32_t hs_node_upsert(hs_handle* h, const hs_node_info* node) {
       else { dy.x = revived[d].x; dy.y = revived[d].y; dy.z = revived[d].z; }
       uint32_t df = DF_PRESENT | (s.health ? (DF_HEALTH | DF_HEALTH_REG) : 0u) | (cordoned.count(s.uuid) ? DF_CORDON : 0u) |
                     ((uint32_t)s.mode_id << 3) | ((uint32_t)(s.network_id >= 0 ? s.network_id : 255) << 8);
+      if (s.sgpu) {
+        df |= DF_SGPU;
+        if (ou != old_usage.end()) {
+          // the pods on the device stay (their classes with them); a QoS switch in flight is retired once the device
+          // registers with the policy it was switching to (JitteryQosCache.Sync, metax/qos.go:37-59)
+          uint32_t keep = (uint32_t)ou->second.w & 0xffff0000u;
+          if (SG_JQ(keep) && SG_JQID(keep) == (uint32_t)s.mode_id) keep &= 0x0fffffffu;
+          df |= keep;
+        }
+      }
       dy.w = (int)df;
       st.x = s.count; st.y = s.devmem; st.z = s.devcore;
       st.w = (int)((uint32_t)s.numa | ((uint32_t)s.type_id << 8) | ((uint32_t)s.index << 14) | ((uint32_t)s.vendor_id << 22) |
@@ -2762,6 +2874,7 @@ int32_t hs_pod_delete(hs_handle* h, const char* pod_uid) {
   mark_dirty(h, it->second.node);
   h->n_parked -= it->second.parked.size();
   if (!it->second.mig.empty()) h->n_mig_pods--;
+  if (it->second.app_class) sgpu_apply_class(h, it->second.node, it->second.n_ent, it->second.app_class, -1);
   const int del_node = it->second.node;
   h->pods.erase(it);
   mig_refresh(h, del_node);
@@ -2802,6 +2915,35 @@ int32_t hs_snapshot_node_mig(hs_handle* h, const char* node, uint32_t* occupied,
     if (health) health[d] = (df & DF_HEALTH) ? 1 : 0;
   }
   return (int32_t)ns.devs.size();
+}
+
+int32_t hs_snapshot_node_sgpu(hs_handle* h, const char* node, int32_t* online, int32_t* offline, const char** pending, uint32_t cap) {
+  if (!h || !node) return HS_ERR_INVALID;
+  HS_IDLE(h);
+  auto it = h->node_by_name.find(node);
+  if (it == h->node_by_name.end()) return HS_ERR_NOTFOUND;
+  const NodeSlot& ns = h->nodes[it->second];
+  for (size_t d = 0; d < ns.devs.size() && d < cap; d++) {
+    const uint32_t df = (uint32_t)h->h_dyn[inv_idx(it->second, (int)d)].w;
+    const bool sg = (df & DF_SGPU) != 0;
+    if (online) online[d] = sg ? (int32_t)SG_ON(df) : 0;
+    if (offline) offline[d] = sg ? (int32_t)SG_OFF(df) : 0;
+    if (pending) pending[d] = (sg && SG_JQ(df) && SG_JQID(df) < h->modes.size()) ? h->modes[SG_JQID(df)].c_str() : nullptr;
+  }
+  return (int32_t)ns.devs.size();
+}
+
+int32_t hs_debug_device_rows(hs_handle* h, const char* node, int32_t device_rows[32], int32_t mirror_rows[32]) {
+  if (!h || !node || !device_rows || !mirror_rows) return HS_ERR_INVALID;
+  HS_IDLE(h);
+  auto it = h->node_by_name.find(node);
+  if (it == h->node_by_name.end()) return HS_ERR_NOTFOUND;
+  cudaSetDevice(h->device);
+  int rc = flush_inventory(h);
+  if (rc != HS_OK) return rc;
+  CUDA_OK(h, cudaMemcpy(device_rows, h->d_dyn + inv_idx(it->second, 0), HS_D * sizeof(int4), cudaMemcpyDeviceToHost));
+  memcpy(mirror_rows, &h->h_dyn[inv_idx(it->second, 0)], HS_D * sizeof(int4));
+  return HS_OK;
 }
 
 int32_t hs_rollback(hs_handle* h, const char* pod_uid) { return hs_pod_delete(h, pod_uid); }

@@ -19,6 +19,8 @@ struct NodeWork {
   float score[HS_D];                                 // DeviceListsScore.Score
   uint32_t order;                                    // nibble i = device slot at list position i
   uint32_t mth_prev;                                 // EF_MTHREADS: device slots the pod's earlier containers (of this phase) received
+  uint32_t sg_picks, sg_excl;                        // EF_SGPU: device slots the pod received so far (mask) / how often each was received whole
+                                                     // (Usedcores 100; 4 bits per slot: ScoreNode's allocatedDevices is a LIST), all containers
   uint32_t kl_cur;                                   // EF_KUNLUN: card indices the pod received so far, all containers (ScoreNode's `current`)
   int aws[HS_D];                                     // EF_NEURON: CustomInfo["awsusageinfo"] of the working copy, -1 = key absent
   int ndev;
@@ -245,6 +247,104 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
     for (int r = 0; r < 24; r++) out.reasons[r] = 0;
     out.fkind = FK_HIST;
     out.fcards = (uint32_t)cnt;
+  }
+  if (e.flags & EF_SGPU) {
+    // metax sGPU, metax/sdevice.go:332-495: filter every device, then prioritise among those that passed
+    const int cls = pod.sg_class & 3;
+    const bool online = cls == 1, reqClassed = cls == 1 || cls == 2;
+    const uint32_t reqq = pod.sg_qos;
+    uint32_t useMaskS = 0xffu, nouseMaskS = 0u;
+    if (e.has_use) useMaskS = uuid_mask_lookup(ka.uuid_pool, e.use_off, e.use_cnt, node);
+    if (e.nouse_cnt) nouseMaskS = uuid_mask_lookup(ka.uuid_pool, e.nouse_off, e.nouse_cnt, node);
+    int cand[HS_D], nc = 0;
+    for (int i = cnt - 1; i >= 0; i--) {
+      const int d = td[i];
+      const uint32_t df = w.dflags[d];
+      if (!(df & DF_HEALTH)) { REASON(15 /*CardUnhealthy*/); continue; }
+      if (w.used[d] != 0) {                                           // checkAppClass, :664-703
+        const bool devOn = SG_ON(df) > 0, devOff = SG_OFF(df) > 0;
+        if (((devOff || devOn) != reqClassed) || (devOn && cls == 2)) { REASON(16 /*CardAppClassMismatch*/); continue; }
+      }
+      if (!online && w.used[d] != 0 && e.coresreq != 100) {           // checkDeviceQos, :527-556: a switch in flight wins over the device's own policy
+        const uint32_t devq = SG_JQ(df) ? SG_JQID(df) : DF_MODE(df);
+        if (devq != 0u && devq != reqq) { REASON(17 /*CardQosPolicyMismatch*/); continue; }
+      }
+      if (!((useMaskS >> d) & 1u) || ((nouseMaskS >> d) & 1u)) { REASON(1); continue; }
+      if (w.count[d] <= w.used[d]) { REASON(2); continue; }
+      if (isMutex && w.used[d] > 0) { REASON(9); continue; }
+      const int memreq = e.memreq > 0 ? e.memreq : (int)((unsigned)w.totmem[d] * (unsigned)e.mempct) / 100;
+      if (w.totmem[d] - w.mem[d] < memreq) { REASON(4); continue; }
+      if (!online) {
+        if (w.totcore[d] - w.cores[d] < e.coresreq) { REASON(5); continue; }
+        if (w.totcore[d] == 100 && e.coresreq == 100 && w.used[d] > 0) { REASON(9); continue; }
+        if (w.totcore[d] != 0 && w.cores[d] == w.totcore[d] && e.coresreq == 0) { REASON(3); continue; }
+      }
+      cand[nc++] = d;
+    }
+    const int nums = e.nums < 0 ? 0 : e.nums;
+    if (nc < nums) {
+      if (MODE == EV_EXPLAIN && nc > 0) out.reasons[12] = (uint32_t)nc;
+      return false;
+    }
+    if (nc > nums) {
+      if (cls != 0) {
+        if (online) {
+          // prioritizeOnlineDevices, :717-770: Go's insertion sort (<= 12 elements) with the online / offline comparator
+          for (int i = 1; i < nc; i++)
+            for (int j = i; j > 0; j--) {
+              const uint32_t a = w.dflags[cand[j]], b = w.dflags[cand[j - 1]];
+              const int ao = (int)SG_ON(a), af = (int)SG_OFF(a), bo = (int)SG_ON(b), bf_ = (int)SG_OFF(b);
+              const bool aOnly = ao == 0 && af > 0, bOnly = bo == 0 && bf_ > 0;
+              bool less;
+              if (aOnly && bOnly) less = af < bf_;
+              else if (aOnly) less = false;
+              else if (bOnly) less = true;
+              else less = ao == bo ? af < bf_ : ao < bo;
+              if (!less) break;
+              const int t = cand[j]; cand[j] = cand[j - 1]; cand[j - 1] = t;
+            }
+        }
+      } else if (e.coresreq == 100) {
+        // prioritizeExclusiveDevices, :583-645: MetaLink zones in ascending id (canonical rule for the Go map), ordered by
+        // size with the same insertion sort; a zone that holds enough cards, else across zones, else unlinked cards
+        int zone_of[HS_D], zsize[HS_D], zones[HS_D], nz = 0;
+        for (int i = 0; i < nc; i++) {
+          const uint32_t df = w.dflags[cand[i]];
+          zone_of[i] = (df & DF_SGPU) ? (int)DF_NET(df) : 0;
+          if (zone_of[i] == 255) zone_of[i] = 0;
+        }
+        for (int i = 0; i < nc; i++) {
+          if (zone_of[i] <= 0) continue;
+          bool seen = false;
+          for (int z = 0; z < nz; z++) if (zones[z] == zone_of[i]) { zsize[z]++; seen = true; }
+          if (!seen) { zones[nz] = zone_of[i]; zsize[nz] = 1; nz++; }
+        }
+        for (int i = 1; i < nz; i++)                 // ascending zone id
+          for (int j = i; j > 0 && zones[j] < zones[j - 1]; j--) { int t = zones[j]; zones[j] = zones[j - 1]; zones[j - 1] = t; t = zsize[j]; zsize[j] = zsize[j - 1]; zsize[j - 1] = t; }
+        for (int i = 1; i < nz; i++)                 // then by size, stable
+          for (int j = i; j > 0 && zsize[j] < zsize[j - 1]; j--) { int t = zones[j]; zones[j] = zones[j - 1]; zones[j - 1] = t; t = zsize[j]; zsize[j] = zsize[j - 1]; zsize[j - 1] = t; }
+        int best[HS_D], nb = 0;
+        for (int z = 0; z < nz && nb == 0; z++)
+          if (zsize[z] >= nums)
+            for (int i = 0; i < nc && nb < nums; i++) if (zone_of[i] == zones[z]) best[nb++] = cand[i];
+        if (nb < nums) {
+          nb = 0;
+          for (int z = 0; z < nz && nb < nums; z++)
+            for (int i = 0; i < nc && nb < nums; i++) if (zone_of[i] == zones[z]) best[nb++] = cand[i];
+          for (int i = 0; i < nc && nb < nums; i++) if (zone_of[i] <= 0) best[nb++] = cand[i];
+        }
+        if (nb >= nums) for (int i = 0; i < nums; i++) cand[i] = best[i];
+      }
+    }
+    for (int t = 0; t < nums && t < HS_D; t++) {
+      const int d = cand[t];
+      fc.tmp_dev[fc.ntmp] = d;
+      fc.tmp_mem[fc.ntmp] = e.memreq > 0 ? e.memreq : (int)((unsigned)w.totmem[d] * (unsigned)e.mempct) / 100;
+      fc.tmp_cores[fc.ntmp] = online ? 0 : e.coresreq;
+      fc.tmp_aws[fc.ntmp] = (int)DF_MODE(w.dflags[d]);      // CustomInfo["QosPolicy"] cloned at Fit time (addJitteryQos compares against it)
+      fc.ntmp++;
+    }
+    return true;
   }
   if (e.flags & EF_ENFLAME) {
     // enflame shared vGCU, enflame/device.go:382-478: the request becomes one profile of the node, then the gates
@@ -733,7 +833,19 @@ __device__ bool dev_fit_container(NodeWork& w, const DevPod& pod, const DevEntry
         if (w.aws[d] < 0) w.aws[d] = 0;
         w.aws[d] += fc.tmp_aws[t];
       }
-      if (e.flags & EF_ENFLAME) {         // enflame/device.go:372-380: Used grows by the profile's slice count
+      if (e.flags & EF_SGPU) {            // metax/sdevice.go:310-330
+        pick_cores = fc.tmp_cores[t];
+        mig_sel = fc.tmp_aws[t] & 7;      // the device's policy at Fit time rides in the row's spare bits (AL_MIG_CAND)
+        w.used[d] += 1;
+        w.cores[d] += pick_cores;
+        w.mem[d] += fc.tmp_mem[t];
+        if ((pod.sg_class & 3) != 1) {    // not an online pod: the working copy's policy becomes the pod's ("" for a whole card)
+          const uint32_t q = pick_cores == 100 ? 0u : (uint32_t)pod.sg_qos;
+          w.dflags[d] = (w.dflags[d] & ~(7u << 3)) | ((q & 7u) << 3);
+        }
+        w.sg_picks |= 1u << d;
+        if (pick_cores == 100 && ((w.sg_excl >> (4 * d)) & 15u) < 15u) w.sg_excl += 1u << (4 * d);   // a card an init AND an app container took counts twice
+      } else if (e.flags & EF_ENFLAME) {         // enflame/device.go:372-380: Used grows by the profile's slice count
         pick_cores = fc.tmp_cores[t];
         mig_sel = fc.tmp_aws[t] & 15;     // reported like a MIG pick: the candidate index in the row's spare bits
         int s = fc.tmp_aws[t] >> 8;
@@ -803,6 +915,11 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   const bool base_key[2] = {(nflags & NF_BASE_NV) != 0, (nflags & NF_BASE_MLU) != 0};
   w.mth_prev = 0;
   w.kl_cur = 0;
+  w.sg_picks = 0; w.sg_excl = 0;
+  uint32_t sg_idle = 0;               // metax sGPU ScoreNode's `previous`: the devices idle before the pod (base usage)
+  int sg_slot = -1;
+  for (int e = 0; e < pod.n_entries; e++) if (ent[e].flags & EF_SGPU) sg_slot = ent[e].score_slot;
+  if (sg_slot >= 0) for (int d = 0; d < w.ndev; d++) if (w.used[d] == 0) sg_idle |= 1u << d;
   uint32_t kl_prev = 0;               // kunlun ScoreNode's `previous`: cards in use before the pod (score.SnapshotDevice, score.go:328)
   bool has_kunlun = false;
   for (int e = 0; e < pod.n_entries; e++) if ((ent[e].flags & EF_KUNLUN) && !(ent[e].flags & EF_VXPU)) has_kunlun = true;
@@ -812,7 +929,7 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
   uint32_t plain_slots = 0;           // … to a vastai type: ScoreNode is the plain sum, no weight (vastai/device.go:181-216)
   for (int e = 0; e < pod.n_entries; e++) {
     if ((ent[e].flags & EF_METAX) && ent[e].score_slot >= 0) metax_slots |= 1u << ent[e].score_slot;
-    if ((ent[e].flags & EF_VASTAI) && ent[e].score_slot >= 0) plain_slots |= 1u << ent[e].score_slot;
+    if ((ent[e].flags & (EF_VASTAI | EF_SGPU)) && ent[e].score_slot >= 0) plain_slots |= 1u << ent[e].score_slot;
   }
 
   if (pod.n_init > 0) {
@@ -849,6 +966,32 @@ __device__ bool dev_score_node(NodeWork& w, const DevPod& pod, const DevEntry* e
     if (!dev_fit_container<MODE>(w, pod, ent, eb, ee, node, nflags, ka, out, score_acc, &score_zero, qa)) return false;
     if (qa) for (int v = 0; v < 2; v++) if (base_key[v] && qa->len[v] == app_index) qa->len[v]++;  // score.go:278-282
     app_index++;
+  }
+  if (sg_slot >= 0 && w.sg_picks != 0u) {
+    // MetaxSDevices.ScoreNode (metax/sdevice.go:295-304), then OverrideScore's +-10000 (policy/node_policy.go:82-88)
+    int result = 0;
+    if ((pod.sg_class & 3) == 1) {                              // scoreOnlineDevices, :772-811
+      for (int d = 0; d < w.ndev; d++) {
+        if (!((w.sg_picks >> d) & 1u)) continue;
+        const int on = (int)SG_ON(w.dflags[d]), off = (int)SG_OFF(w.dflags[d]);
+        result += (off > 0 && on == 0) ? -100 * off : (-20 * on - 2 * off);
+      }
+    } else if (w.sg_excl != 0u && (pod.sg_class & 4)) {          // topologyAwareEnable :647-667, scoreExclusiveDevices :669-
+      auto zone = [&](int d) { const uint32_t df = w.dflags[d]; const int z = (df & DF_SGPU) ? (int)DF_NET(df) : 0; return z == 255 ? 0 : z; };
+      uint32_t exmask = 0;
+      for (int d = 0; d < w.ndev; d++) if ((w.sg_excl >> (4 * d)) & 15u) exmask |= 1u << d;
+      auto pairs = [&](uint32_t mask, bool counted) {            // LinkDevices.Score, metax/score.go:27-57 (equal uuids score 0)
+        int s = 0;
+        for (int a = 0; a < w.ndev; a++)
+          for (int b = a + 1; b < w.ndev; b++)
+            if (((mask >> a) & 1u) && ((mask >> b) & 1u) && zone(a) != 0 && zone(a) == zone(b))
+              s += counted ? 10 * (int)((w.sg_excl >> (4 * a)) & 15u) * (int)((w.sg_excl >> (4 * b)) & 15u) : 10;
+        return s;
+      };
+      const int availableScore = pairs(sg_idle, false), allocatedScore = pairs(exmask, true), restScore = pairs(sg_idle & ~exmask, false);
+      result = 10 * allocatedScore - (availableScore - allocatedScore - restScore);
+    }
+    score_acc[sg_slot] = __fmul_rn((pod.flags & PF_NODE_SPREAD) ? -10000.0f : 10000.0f, (float)result);
   }
   // OverrideScore, policy/node_policy.go:67-95: Σ vendor ScoreNode in sorted type-key order
   float devScore = 0.0f;

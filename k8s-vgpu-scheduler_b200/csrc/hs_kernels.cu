@@ -105,6 +105,12 @@ __device__ __forceinline__ void quota_apply(const KernelArgs& ka, const DevPod& 
 // dflags after a change of the MIG bookkeeping (delta.w of a commit / release row): bit 0 = one more (sign +1) or one
 // less cached pod that makes the device fail closed, bit 1 = the covered slices become bits 8-15
 __device__ __forceinline__ uint32_t mig_apply(uint32_t df, int w, int sign) {
+  if ((w >> 2) & 3) {          // metax sGPU: one online (1) / offline (2) pod more or less on the device
+    const int sh = ((w >> 2) & 3) == 1 ? 16 : 22;
+    int c = (int)((df >> sh) & 63u) + sign;
+    c = c < 0 ? 0 : (c > 63 ? 63 : c);
+    return (df & ~(63u << sh)) | ((uint32_t)c << sh);
+  }
   if (w & 2) df = (df & ~(255u << 16)) | (((uint32_t)w >> 8) & 255u) << 16;
   if (w & 1) {
     int bad = (int)DF_BAD(df) + sign;
@@ -730,8 +736,20 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
           collapse_rows(ent, la, my_nalloc, delta);
           const uint32_t off = pod.alloc_base;
           for (uint32_t i = 0; i < my_nalloc && off + i < ka.alloc_cap; i++) ka.allocs[off + i] = la[i];
+          const int sg_cls = pod.sg_class & 3;
+          if (sg_cls == 1 || sg_cls == 2)          // metax sGPU: the pod joins the PodInfos of every device it received (scheduler.go:786)
+            for (uint32_t i = 0; i < my_nalloc; i++)
+              if (ent[AL_ENTRY(la[i])].flags & EF_SGPU) delta[AL_DEV(la[i])].w = sg_cls << 2;
           if (!dry) {
             store_usage(ka, my_node, delta, +1);
+            if (sg_cls != 1)                          // addJitteryQos (metax/sdevice.go:558-581): a QoS switch is now in flight on these devices
+              for (uint32_t i = 0; i < my_nalloc; i++) {
+                if (!(ent[AL_ENTRY(la[i])].flags & EF_SGPU)) continue;
+                const uint32_t expected = la[i].usedcores == 100 ? 0u : ((uint32_t)pod.sg_qos & 7u);
+                if ((uint32_t)AL_MIG_CAND(la[i]) == expected) continue;
+                int4* p = ka.dyn + (size_t)my_node * HS_D + AL_DEV(la[i]);
+                p->w = (int)(((uint32_t)p->w & 0x0fffffffu) | (1u << 28) | (expected << 29));
+              }
             refresh_node_score(ka, my_node);
             quota_apply(ka, pod, my_node, delta, +1);      // quotaManager.AddUsage, scheduler.go:1136-1138
           }

@@ -31,6 +31,12 @@
 #define DF_MODE(x) (((x) >> 3) & 7u)
 #define DF_NET(x) (((x) >> 8) & 255u)
 #define DF_HEALTH_REG 64u
+#define DF_SGPU 128u                // a metax sGPU device: bits 3-5 = its registered QoS policy (mode table id), bits 8-15 = its MetaLink zone,
+                                    // bits 16-21 / 22-27 = online / offline pods on it, bit 28 + bits 29-31 = a QoS switch in flight and its target
+#define SG_ON(x) (((x) >> 16) & 63u)
+#define SG_OFF(x) (((x) >> 22) & 63u)
+#define SG_JQ(x) (((x) >> 28) & 1u)
+#define SG_JQID(x) (((x) >> 29) & 7u)
 #define DF_MODE_MIG 2u              // index of "mig" in the handle's mode table (fixed: "", "hami-core", "mig", "mps")
 #define DF_OCC(x) (((x) >> 16) & 255u)
 #define DF_BAD(x) ((x) >> 24)
@@ -71,6 +77,7 @@ enum { CK_NONE = 0, CK_BINPACK = 1, CK_SPREAD = 2, CK_NUMA = 3 };
 #define EF_KUNLUN 1024u    // kunlun whole XPUs (kunlun/device.go:184-240, topo.go): graghSelect over list positions, slot-only usage, ScoreNode by wings
 #define EF_VXPU 2048u      // with EF_KUNLUN: the shared "XPU" type (kunlun/vdevice.go:231-306): FitVXPU, full usage, no ScoreNode
 #define EF_ENFLAME 4096u   // enflame shared vGCU (enflame/device.go:382-478): one DRS profile per request from the node's table, then the gates
+#define EF_SGPU 8192u      // metax sGPU (metax/sdevice.go:332-495): filter by class / QoS / template gates, then prioritise; policy-neutral ScoreNode
 #define EF_COUNT_ONLY 8u   // biren's Fit (biren/device.go:190-248): gates end after mutex; the pick has Usedmem 0, Usedcores = Coresreq
 
 struct DevEntry {           // one ContainerDeviceRequest (devices.go:222-228), 64 B
@@ -113,7 +120,8 @@ struct DevPod {             // one op of the stream, 96 B + entries
   uint32_t entry_off;       // first DevEntry in the entry pool
   uint8_t ctr_begin[HS_MAX_C + 1]; // container c owns entries [ctr_begin[c], ctr_begin[c+1])
   uint8_t win_len;          // ops from this one on that may be decided as ONE window (hs_window.cuh); < 2 = decide it alone
-  uint8_t pad3[2];
+  uint8_t sg_class;         // metax sGPU: bits 0-1 metax-tech.com/sgpu-app-class (0 absent, 1 online, 2 offline, 3 another value), bit 2 topology awareness on
+  uint8_t sg_qos;           // … metax-tech.com/sgpu-qos-policy as a mode table id ("" = 0, a value the table does not hold = 7)
   // OP_RELEASE: subtract a committed allocation.
   int32_t rel_node;         // node slot, or -1 = take node and deltas from decision `rel_ref` of this batch
   int32_t rel_ref;

@@ -17,7 +17,7 @@ _lib = None
 EXPORTS = [
     "hs_create", "hs_destroy", "hs_last_error", "hs_node_upsert", "hs_node_remove", "hs_node_count",
     "hs_usage_apply", "hs_pod_delete", "hs_filter", "hs_run_batch", "hs_run_batch_async", "hs_batch_wait", "hs_batch_get", "hs_rollback",
-    "hs_snapshot_node", "hs_pod_get", "hs_pod_set_mig", "hs_snapshot_node_mig", "hs_decode_mig_allocations", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
+    "hs_snapshot_node", "hs_pod_get", "hs_pod_set_mig", "hs_snapshot_node_mig", "hs_snapshot_node_sgpu", "hs_debug_device_rows", "hs_decode_mig_allocations", "hs_last_device_ms", "hs_launch_count", "hs_batch_summary", "hs_sweep_probe",
     "hs_shard_unique_id", "hs_shard_init", "hs_sweep_static", "hs_shard_mailbox", "hs_shard_connect",
     "hs_decode_node_devices", "hs_decode_pod_devices", "hs_collapse_pod_devices", "hs_node_register", "hs_pod_ingest", "hs_pod_shrink", "hs_filter_dry", "hs_filter_simulate", "hs_quota_set", "hs_quota_del", "hs_quota_get", "hs_quota_memory_factor", "hs_generate_requests", "hs_debug_timing", "hs_debug_window_stats", "hs_debug_decision_ns", "hs_debug_copy_bytes", "hs_debug_host_seconds", "hs_debug_divcheck", "hs_debug_metax_table",
 ]
@@ -382,6 +382,20 @@ class Engine:
         hl = (C.c_uint8 * cap)()
         n = self.L.hs_snapshot_node_mig(self.h, abi._b(node), occ, hl, cap)
         return [(occ[i], hl[i]) for i in range(max(0, min(n, cap)))]
+
+    def device_rows(self, node):
+        """(device rows, host mirror rows) of one node: 8 x (used, usedmem, usedcores, dflags) each (test hook)."""
+        dev, mir = (C.c_int32 * 32)(), (C.c_int32 * 32)()
+        self.L.hs_debug_device_rows.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+        self._check(self.L.hs_debug_device_rows(self.h, abi._b(node), dev, mir))
+        return [tuple(dev[i * 4:i * 4 + 4]) for i in range(8)], [tuple(mir[i * 4:i * 4 + 4]) for i in range(8)]
+
+    def snapshot_node_sgpu(self, node, cap=16):
+        """[(online pods, offline pods, pending QoS or None)] per device of the node (metax sGPU bookkeeping)."""
+        on, off, pend = (C.c_int32 * cap)(), (C.c_int32 * cap)(), (C.c_char_p * cap)()
+        self.L.hs_snapshot_node_sgpu.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_char_p), C.c_uint32]
+        n = self.L.hs_snapshot_node_sgpu(self.h, abi._b(node), on, off, pend, cap)
+        return [(on[i], off[i], pend[i].decode() if pend[i] is not None else None) for i in range(max(0, min(n, cap)))]
 
     def decision_ns(self, n):
         """%globaltimer ns at which each Filter decision of the last run_batch became final (0 = not a Filter)."""

@@ -1669,6 +1669,12 @@ class PlainDevices : public Devices {
   }
 
   bool PolicyNeutralScore() const override { return v_.FitKind == 11; }      // metax/sdevice.go:305-308
+  bool PendingQos(const std::string& uuid, std::string& out) const override {
+    auto it = sgpu_.jq.find(uuid);
+    if (it == sgpu_.jq.end()) return false;
+    out = it->second;
+    return true;
+  }
   void SyncRegistered(const std::vector<DeviceInfo>& devices) const override {      // JitteryQosCache.Sync, metax/qos.go:37-59
     if (v_.FitKind != 11) return;
     for (auto& d : devices) {

@@ -232,6 +232,7 @@ class Devices {
   virtual bool PolicyNeutralScore() const { return false; }
   // GetNodeDevices side effect of the metax sGPU vendor: jqCache.Sync (metax/sdevice.go:131-139, qos.go:37-59)
   virtual void SyncRegistered(const std::vector<DeviceInfo>&) const {}
+  virtual bool PendingQos(const std::string& uuid, std::string& out) const { (void)uuid; (void)out; return false; }
 };
 
 struct AscendTemplate { std::string Name; int64_t Memory = 0; };

@@ -269,6 +269,23 @@ float oracle_sgpu_score(oracle_handle* o, const hs_alloc_entry* picks, uint32_t 
   for (uint32_t i = 0; i < n_prev; i++) previous.push_back(toDls(prev[i]).Device);
   return v->ScoreNode(psd, "", nullptr, &previous);
 }
+int32_t oracle_snapshot_node_sgpu(oracle_handle* o, const char* node, int32_t* online, int32_t* offline, const char** pending, uint32_t cap) {
+  auto snap = o->s->Snapshot(str(node));
+  const Devices* v = o->s->Vendor("Metax-SGPU");
+  Arena& a = o->arena;
+  a.clear();
+  uint32_t n = 0;
+  for (auto& d : snap) {
+    if (n < cap) {
+      if (online) online[n] = d.OnlinePods;
+      if (offline) offline[n] = d.OfflinePods;
+      std::string q;
+      if (pending) pending[n] = (v && d.HasSgpu && v->PendingQos(d.ID, q)) ? a.s(q) : nullptr;
+    }
+    n++;
+  }
+  return (int32_t)n;
+}
 float oracle_kunlun_calc_score(const int32_t* prev, uint32_t n_prev, const int32_t* cur, uint32_t n_cur) {
   auto dedup = [](const int32_t* v, uint32_t n) {       // addidx, kunlun/topo.go:40-48
     std::vector<int> out;

@@ -49,6 +49,7 @@ int32_t oracle_pod_delete(oracle_handle* o, const char* pod_uid);
 /* MetaxSDevices.ScoreNode (metax/sdevice.go:295-304) before OverrideScore's +-10000 weight */
 float   oracle_sgpu_score(oracle_handle* o, const hs_alloc_entry* picks, uint32_t n_picks, const int32_t* zones,
                           const oracle_dev* prev, uint32_t n_prev, const hs_kv* annos, uint32_t n_annos);
+int32_t oracle_snapshot_node_sgpu(oracle_handle* o, const char* node, int32_t* online, int32_t* offline, const char** pending, uint32_t cap);
 float   oracle_kunlun_calc_score(const int32_t* prev, uint32_t n_prev, const int32_t* cur, uint32_t n_cur);
 /* dynamic MIG: the informer side and the state getNodesUsage derives (see hs_pod_set_mig / hs_snapshot_node_mig) */
 int32_t oracle_pod_set_mig(oracle_handle* o, const char* pod_uid, const hs_mig_reservation* res, uint32_t n);

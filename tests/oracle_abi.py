@@ -216,6 +216,12 @@ class Oracle:
         n = self.L.oracle_snapshot_node_mig(self.h, abi._b(node), occ, hl, cap)
         return [(occ[i], hl[i]) for i in range(max(0, n))]
 
+    def snapshot_node_sgpu(self, node, cap=16):
+        on, off, pend = (C.c_int32 * cap)(), (C.c_int32 * cap)(), (C.c_char_p * cap)()
+        self.L.oracle_snapshot_node_sgpu.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_char_p), C.c_uint32]
+        n = self.L.oracle_snapshot_node_sgpu(self.h, abi._b(node), on, off, pend, cap)
+        return [(on[i], off[i], pend[i].decode() if pend[i] is not None else None) for i in range(max(0, n))]
+
     def pod_get(self, uid):
         rows = (abi.hs_pod_usage_row * 16)()
         node = C.c_char_p()

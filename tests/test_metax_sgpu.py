@@ -107,3 +107,114 @@ def test_score_exclusive_table(orc, case):
 def test_score_online_table(orc, case):
     # sdevice_test.go:2775-2945 (TestScoreOnlineDevices)
     assert _score(orc, case["pickDevs"], case["devs"], {CLASS: "online"}) == case["expectedScore"]
+
+
+# ---- GPU parity ------------------------------------------------------------------------------------------------------
+def sgpu_node(rng, name, cards=8):
+    devs = []
+    for i in range(cards):
+        devs.append({"id": "%s-sgpu-%d" % (name, i), "index": i, "count": rng.choice([4, 8, 16]), "devmem": 65536, "devcore": 100,
+                     "type": SGPU, "numa": i // 4, "mode": "", "health": rng.random() > 0.04, "vendor": SGPU,
+                     "sgpu": {"qos_policy": rng.choice(["", "best-effort", "fixed-share", "burst-share", "best-effort"]),
+                              "link_zone": rng.choice([0, 1, 1, 2, 2, 3])}})
+    return {"name": name, "devices": devs}
+
+
+def sgpu_pod(rng, uid):
+    annos = {}
+    r = rng.random()
+    if r < 0.2:
+        annos[CLASS] = "online"
+    elif r < 0.35:
+        annos[CLASS] = "offline"
+    if annos.get(CLASS) != "online":
+        annos[QOS] = rng.choice(["best-effort", "best-effort", "fixed-share", "burst-share"])
+    if rng.random() < 0.5:
+        annos[TOPO] = rng.choice(["true", "true", "false", "bogus"])
+    if rng.random() < 0.08:
+        annos["hami.io/gpu-scheduler-policy"] = "mutex"
+    if rng.random() < 0.1:
+        annos["hami.io/node-scheduler-policy"] = rng.choice(["spread", "binpack"])
+    classed = CLASS in annos
+    nums = 1 if classed else rng.choice([1, 1, 2, 2, 4])
+    whole = (not classed) and rng.random() < 0.45
+    req = {"key": SGPU, "type": SGPU, "nums": nums, "memreq": 0 if whole else rng.choice([0, 4096, 16384]),
+           "mempct": 100, "coresreq": 100 if whole else rng.choice([0, 10, 30, 50])}
+    if req["memreq"]:
+        req["mempct"] = 0
+    ctrs = [[req]]
+    if not classed and rng.random() < 0.2:
+        ctrs.append([{"key": SGPU, "type": SGPU, "nums": 1, "memreq": 2048, "mempct": 0, "coresreq": rng.choice([10, 100])}])
+    pod = {"uid": uid, "ns": "default", "name": uid, "annotations": annos, "containers": ctrs, "n_init": 0}
+    if len(ctrs) > 1 and rng.random() < 0.3:
+        pod["n_init"] = 1
+    return pod
+
+
+def sgpu_cluster(seed, n_nodes=24, n_pods=900, topo_default=False):
+    rng = random.Random(seed)
+    nodes = [sgpu_node(rng, "mx-%02d" % i, cards=rng.choice([2, 4, 8, 8])) for i in range(n_nodes)]
+    ops, live = [], []
+    for p in range(n_pods):
+        if live and rng.random() < 0.3:
+            ops.append(("delete", live.pop(rng.randrange(len(live)))))
+            continue
+        uid = "pod-%04d" % p
+        ops.append(("filter", sgpu_pod(rng, uid)))
+        live.append(uid)
+    return {"node_policy": rng.choice(["binpack", "spread"]), "gpu_policy": rng.choice(["binpack", "spread"])}, nodes, ops
+
+
+def _vendors(topo_default):
+    v = [list(x) for x in abi.DEFAULT_VENDORS]
+    for x in v:
+        if x[0] == SGPU:
+            while len(x) < 9:
+                x.append(None)
+            x[8] = 1 if topo_default else 0
+    return [tuple(x) for x in v]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,topo_default", [(4, False), (7, True)])
+def test_metax_sgpu_gpu_parity(seed, topo_default):
+    import parity
+    import k8s_vgpu_scheduler_b200.engine as eng
+    cfg, nodes, ops = sgpu_cluster(seed)
+    o = oa.Oracle(cfg["node_policy"], cfg["gpu_policy"], vendors=_vendors(topo_default))
+    e = eng.Engine(cfg["node_policy"], cfg["gpu_policy"], vendors=_vendors(topo_default))
+    for n in nodes:
+        o.node_upsert(n)
+        e.node_upsert(n)
+    ref, got = [], []
+    rng = random.Random(seed + 100)
+    for s in range(0, len(ops), 150):
+        part = ops[s:s + 150]
+        for kind, arg in part:
+            ref.append(o.filter(arg) if kind == "filter" else {"status": o.pod_delete(arg)})
+        e.run_batch(eng.PackedOps(part))
+        got += [e.batch_get(i) for i in range(len(part))]
+        assert parity.compare(ops[:len(ref)], ref, got) == [], "batch at %d" % s
+        for n in nodes:
+            assert e.snapshot(n["name"]) == o.snapshot(n["name"])
+            assert e.snapshot_node_sgpu(n["name"]) == o.snapshot_node_sgpu(n["name"]), (s, n["name"])
+            dev_rows, mirror_rows = e.device_rows(n["name"])
+            assert dev_rows == mirror_rows, (s, n["name"], [(hex(a[3] & 0xffffffff), hex(b[3] & 0xffffffff)) for a, b in zip(dev_rows, mirror_rows) if a != b])
+        # the device plugin catches up with some of the QoS switches: those nodes register again with the new policy
+        # (JitteryQosCache.Sync retires the switch), others with the old one (the switch stays in flight)
+        for n in rng.sample(nodes, 5):
+            for d in n["devices"]:
+                if rng.random() < 0.5:
+                    d["sgpu"]["qos_policy"] = rng.choice(["", "best-effort", "fixed-share", "burst-share"])
+            o.node_upsert(n)
+            e.node_upsert(n)
+    fits = [r for (k, a), r in zip(ops, ref) if k == "filter" and r["status"] == abi.HS_FIT]
+    nofit = [r for (k, a), r in zip(ops, ref) if k == "filter" and r["status"] == abi.HS_NOFIT]
+    assert len(fits) > 250 and len(nofit) > 20
+    reasons = " ".join(v for r in nofit for v in r["failed"].values())
+    assert "CardQosPolicyMismatch" in reasons and "CardAppClassMismatch" in reasons
+    assert len({round(r["score"], 1) for r in fits}) > 20
+    assert any(abs(r["score"]) > 5000 for r in fits)                 # the +-10000 weight was in play
+    assert all("metax-tech.com/gpu-devices-allocated" in r["annotations"] for r in fits)
+    e.close()
+    o.close()
