@@ -88,6 +88,7 @@ type VendorConfig struct {
 	FitKind                                                        int32
 	UseUUIDKey, NoUseUUIDKey, ToAllocateKey, AllocatedKey          string
 	UseTypeKey, NoUseTypeKey                                       string
+	Option                                                         int32 // HS_FIT_METAX_SGPU: 1 = MetaxConfig.TopologyAware
 }
 
 // New replaces newScheduler + config.InitDevicesWithConfig for this path (cmd/scheduler/main.go:70-71 flags).
@@ -138,6 +139,7 @@ func New(nodePolicy, gpuPolicy string, ascend []AscendConfig, vendors []VendorCo
 			arr[i].allocated_key = opt(v.AllocatedKey)
 			arr[i].use_type_key = opt(v.UseTypeKey)
 			arr[i].nouse_type_key = opt(v.NoUseTypeKey)
+			arr[i].option = C.int32_t(v.Option)
 		}
 		cfg.vendors = &arr[0]
 		cfg.n_vendors = C.uint32_t(len(vendors))
@@ -210,6 +212,19 @@ func (e *Engine) UpsertNode(info *device.NodeInfo, cordon string, hasCordon bool
 		}
 		if len(d.DevicePairScore.Scores) > 0 {
 			anyPair = true
+		}
+		if qos, ok := d.CustomInfo["QosPolicy"]; ok { // metax sGPU: CustomInfo of convertMetaxSDeviceToHAMIDevice (metax/protocol.go:108-112)
+			sg := (*C.hs_metax_sgpu_info)(a.alloc(1, unsafe.Sizeof(C.hs_metax_sgpu_info{})))
+			sg.qos_policy = a.str(fmt.Sprint(qos))
+			switch z := d.CustomInfo["LinkZone"].(type) {
+			case int32:
+				sg.link_zone = C.int32_t(z)
+			case int:
+				sg.link_zone = C.int32_t(z)
+			case float64:
+				sg.link_zone = C.int32_t(z)
+			}
+			arr[i].sgpu = sg
 		}
 		if profiles, ok := d.CustomInfo["profiles"]; ok { // enflame shared vGCU: CustomInfo of GetNodeDevices (enflame/device.go:235-252)
 			ef := (*C.hs_enflame_info)(a.alloc(1, unsafe.Sizeof(C.hs_enflame_info{})))

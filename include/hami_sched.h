@@ -331,7 +331,7 @@ enum { HS_FIT_TEMPLATE = 0, HS_FIT_COUNT_ONLY = 1, HS_FIT_AMD = 2,
         * container with a device, assigned-containers = {"<container name>": {"allocated":false,"request":<slices>,
         * "profileID":…,"profileName":…}} (hs_container.name).                                                          */
        HS_FIT_ENFLAME_VGCU = 10,
-       /* metax sGPU, type "Metax-SGPU" (pkg/device/metax/sdevice.go:295-495).  Filter, then prioritise.  A device passes
+       /* metax sGPU, type "Metax-SGPU" (pkg/device/metax/sdevice.go:332-495).  Filter, then prioritise.  A device passes
         * when it is healthy ("CardUnhealthy"), its application class agrees with the pod's
         * metax-tech.com/sgpu-app-class (a device in use runs either online/offline pods or plain ones, and an offline pod
         * never joins a device with online pods: "CardAppClassMismatch"), — unless the pod is online — its QoS policy

@@ -1923,7 +1923,7 @@ void absorb_results(hs_handle* h, int first, int last) {
         pr.app_class = (uint8_t)m.sg_class;
         sgpu_apply_class(h, dec.node, pr.n_ent, m.sg_class, +1);
       }
-      if (m.sg_class != 1)                                  // … and addJitteryQos leaves a QoS switch in flight (metax/sdevice.go:558-581)
+      if (m.sg_class != 1)                                  // … and addJitteryQos leaves a QoS switch in flight (metax/sdevice.go:558-577)
         for (uint32_t i = 0; i < dec.n_alloc; i++) {
           const DevAlloc& a = h->b_alloc.h[dec.alloc_off + i];
           int4& v = h->h_dyn[inv_idx(dec.node, AL_DEV(a))];

@@ -401,6 +401,46 @@ bool decode_node_json(const std::string& s, std::vector<Device>& out, std::strin
 // false on ANY error, as the caller there turns every error into 0: a syntax error, a document that is not an object
 // (null is fine and leaves the map empty), a key strconv.ParseInt rejects, a value that is not an integer number
 // (null is fine and stores 0).  A later duplicate key wins.
+// metax sGPU: json.Unmarshal into []*MetaxSDeviceInfo, then convertMetaxSDeviceToHAMIDevice (protocol.go:96-116)
+bool metax_sgpu_devices(const std::string& json, std::vector<Device>& out, std::string& err) {
+  out.clear();
+  JParser p(json);
+  JV doc;
+  if (!p.document(doc)) { err = p.err; return false; }
+  if (doc.kind != JV::Arr && doc.kind != JV::Null) { err = std::string("json: cannot unmarshal ") + kind_name(doc) + " into Go value of type []*metax.MetaxSDeviceInfo"; return false; }
+  size_t idx = 0;
+  for (const JV& el : doc.a) {
+    Device d;
+    if (el.kind == JV::Null) { err = "null device entry in node annotation"; return false; }
+    if (el.kind != JV::Obj) { err = std::string("json: cannot unmarshal ") + kind_name(el) + " into Go value of type metax.MetaxSDeviceInfo"; return false; }
+    d.index = (uint32_t)idx;
+    d.type = "Metax-SGPU";
+    d.has_sgpu = true;
+    for (const auto& f : el.o) {
+      const JV& v = f.second;
+      int64_t x = 0;
+      auto i32 = [&](const char* field, int32_t& dst) {
+        if (v.kind == JV::Null) return true;
+        if (v.kind == JV::Num && num_to_int(v, 32, false, x)) { dst = (int32_t)x; return true; }
+        err = std::string("json: cannot unmarshal ") + kind_name(v) + " into Go struct field MetaxSDeviceInfo." + field + " of type int32";
+        return false;
+      };
+      if (key_is(f.first, "uuid")) { if (v.kind == JV::Str) d.id = v.s; else if (v.kind != JV::Null) { err = "json: cannot unmarshal into Go struct field MetaxSDeviceInfo.uuid of type string"; return false; } }
+      else if (key_is(f.first, "totalDevCount")) { if (!i32("totalDevCount", d.count)) return false; }
+      else if (key_is(f.first, "totalCompute")) { if (!i32("totalCompute", d.devcore)) return false; }
+      else if (key_is(f.first, "totalVRam")) { if (!i32("totalVRam", d.devmem)) return false; }
+      else if (key_is(f.first, "numa")) { if (!i32("numa", d.numa)) return false; }
+      else if (key_is(f.first, "linkZone")) { if (!i32("linkZone", d.sgpu_link_zone)) return false; }
+      else if (key_is(f.first, "healthy")) { if (v.kind == JV::Bool) d.health = v.b; else if (v.kind != JV::Null) { err = "json: cannot unmarshal into Go struct field MetaxSDeviceInfo.healthy of type bool"; return false; } }
+      else if (key_is(f.first, "qosPolicy")) { if (v.kind == JV::Str) d.sgpu_qos = v.s; else if (v.kind != JV::Null) { err = "json: cannot unmarshal into Go struct field MetaxSDeviceInfo.qosPolicy of type string"; return false; } }
+    }
+    out.push_back(d);
+    idx++;
+  }
+  if (out.empty()) { err = "no sdevice found on node"; return false; }
+  return true;
+}
+
 // enflame GetNodeDevices, enflame/device.go:198-252 (parseProfile :621-643, parseDRSCapacity :659-683)
 static void enf_profile_parts(const std::string& name, int64_t& size, int64_t& mem_gb) {
   size = 0; mem_gb = 0;

@@ -25,6 +25,10 @@ struct Device {            // device.DeviceInfo, the fields the scheduler path r
   bool has_mig_profiles = false;
   std::vector<MigProfileRec> mig_profiles;   // DeviceInfo.MIGProfiles
   bool die_strategy = false; // CustomInfo["DeviceStrategy"] == "die" (vastai die mode)
+  // metax sGPU CustomInfo (metax/protocol.go:108-112)
+  bool has_sgpu = false;
+  std::string sgpu_qos;
+  int32_t sgpu_link_zone = 0;
   // enflame DRS CustomInfo (enflame/device.go:235-252)
   bool has_enflame = false;
   std::string enf_minor, enf_index;
@@ -54,6 +58,8 @@ bool neuron_devices_from_capacity(const std::string& node, int64_t counts, int64
 // to no reservation; false + err on malformed JSON, an incomplete entry, a partial runtime identity or a duplicate
 // (containerIndex, deviceIndex) — the caller then treats the pod as carrying no reservation (scheduler.go:760-766)
 bool decode_mig_allocations(const std::string& json, std::vector<MigReservationRec>& out, std::string& err);
+// metax sGPU GetNodeDevices (metax/sdevice.go:131-140,506-526; protocol.go:50-64,96-116): metax-tech.com/node-gpu-devices
+bool metax_sgpu_devices(const std::string& json, std::vector<Device>& out, std::string& err);
 // enflame GetNodeDevices (enflame/device.go:198-252): the node's enflame.com/gcu-drs-capacity annotation
 bool enflame_devices_from_drs(const std::string& json, const std::string& node, std::vector<Device>& out, std::string& err);
 // json.Unmarshal into map[int]int as parseMetaxAnnos uses it (metax/device.go:168-183): false on any error

@@ -742,7 +742,7 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
               if (ent[AL_ENTRY(la[i])].flags & EF_SGPU) delta[AL_DEV(la[i])].w = sg_cls << 2;
           if (!dry) {
             store_usage(ka, my_node, delta, +1);
-            if (sg_cls != 1)                          // addJitteryQos (metax/sdevice.go:558-581): a QoS switch is now in flight on these devices
+            if (sg_cls != 1)                          // addJitteryQos (metax/sdevice.go:558-577): a QoS switch is now in flight on these devices
               for (uint32_t i = 0; i < my_nalloc; i++) {
                 if (!(ent[AL_ENTRY(la[i])].flags & EF_SGPU)) continue;
                 const uint32_t expected = la[i].usedcores == 100 ? 0u : ((uint32_t)pod.sg_qos & 7u);

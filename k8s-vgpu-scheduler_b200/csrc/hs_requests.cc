@@ -32,6 +32,30 @@ const hs_quantity* lookup_limits(const hs_container_resources* c, const char* na
 
 // returns false for the zero-value ContainerDeviceRequest{}
 bool generate(const hs_vendor_resources& v, const hs_container_resources* c, hs_container_request& r) {
+  if (v.kind == HS_REQ_METAX_SGPU) {
+    // metax/sdevice.go:222-293: Limits only; vcore defaults to 100; vmemory in Gi unless the quantity carries a unit
+    r.key = v.common_word; r.type = v.common_word;
+    const hs_quantity* q = lookup_limits(c, v.count_name);
+    if (!q || !q->as_int64_ok) return false;
+    if (q->as_int64 <= 0 || q->as_int64 > kMaxInt32) return false;
+    int64_t core = 100, mem = 0;
+    const hs_quantity* cq = lookup_limits(c, v.cores_name);
+    if (cq && cq->as_int64_ok) {
+      if (cq->as_int64 < 0 || cq->as_int64 > kMaxInt32) return false;
+      core = cq->as_int64;
+    }
+    const hs_quantity* mq = lookup_limits(c, v.memory_name);
+    if (mq && mq->as_int64_ok) {
+      if (mq->has_suffix) mem = mq->as_int64 / 1024 / 1024;
+      else {
+        if (mq->as_int64 < 0 || mq->as_int64 > kMaxInt32 / 1024) return false;
+        mem = mq->as_int64 * 1024;
+      }
+      if (mem < 0 || mem > kMaxInt32) return false;
+    }
+    r.nums = (int32_t)q->as_int64; r.memreq = (int32_t)mem; r.mempct = mem == 0 ? 100 : 0; r.coresreq = (int32_t)core;
+    return true;
+  }
   if (v.kind == HS_REQ_ENFLAME) {
     // enflame/device.go:322-366: a positive enflame.com/drs-gcu count is a DIRECT slice request; otherwise memory / core by
     // spec (getContainerResourceRequest :747-758: Quantity.Value() of Limits, then Requests)
@@ -200,7 +224,8 @@ bool generate(const hs_vendor_resources& v, const hs_container_resources* c, hs_
       corenum = corenum / (int32_t)n;
       break;
     }
-    case HS_REQ_ENFLAME:                                      // handled before the count lookup (two request shapes)
+    case HS_REQ_METAX_SGPU:
+    case HS_REQ_ENFLAME:                                      // handled before the count lookup (their own request shapes)
       return false;
     case HS_REQ_KUNLUN_VXPU: {                                // kunlun/vdevice.go:173-213: memory rounded up to 24576 / 49152 / 98304
       if (mem && mem->as_int64_ok) memnum = mem->as_int64 <= 24576 ? 24576 : (mem->as_int64 <= 49152 ? 49152 : 98304);   // trimMemory, :62-70

@@ -122,6 +122,10 @@ def decode_node_devices(vendor, fmt, annotation, pair_scores=None, node_name=Non
             ef = devs[i].enflame.contents
             out[i]["Enflame"] = {"minor": ef.minor.decode(), "index": ef.index.decode(), "max_slice": ef.max_slice,
                                  "profiles": {ef.profiles[k].key.decode(): ef.profiles[k].value.decode() for k in range(ef.n_profiles)}}
+    for i in range(n.value):      # metax sGPU CustomInfo (QosPolicy, LinkZone)
+        if devs[i].sgpu:
+            sg = devs[i].sgpu.contents
+            out[i]["Sgpu"] = {"qos_policy": (sg.qos_policy or b"").decode(), "link_zone": sg.link_zone}
     for i in range(n.value):      # DeviceInfo.MIGProfiles, present for GPUs that report any
         if devs[i].n_mig_profiles:
             out[i]["MigProfiles"] = [

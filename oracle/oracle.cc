@@ -1298,12 +1298,12 @@ FitResult fitEnflame(const std::vector<DeviceUsage*>& devices, const ContainerDe
   return r;
 }
 
-// ---- metax sGPU ("Metax-SGPU", metax/sdevice.go:295-495): filter, then prioritise ------------------------------------
+// ---- metax sGPU ("Metax-SGPU", metax/sdevice.go:332-495): filter, then prioritise ------------------------------------
 struct SgpuState {                      // the vendor object's jqCache (metax/qos.go): device UUID -> the QoS it is about to switch to
   std::map<std::string, std::string> jq;
 };
 static const std::string* podAnno(const Pod& pod, const char* key) { return anno(pod, key); }
-static bool sgpuCheckAppClass(const std::string& requestClass, const DeviceUsage& dev) {    // checkAppClass, sdevice.go:664-703
+static bool sgpuCheckAppClass(const std::string& requestClass, const DeviceUsage& dev) {    // checkAppClass, sdevice.go:738-775
   if (dev.Used == 0) return true;
   const bool devOnline = dev.OnlinePods > 0, devOffline = dev.OfflinePods > 0;
   if ((devOffline || devOnline) == (requestClass == "offline" || requestClass == "online")) {

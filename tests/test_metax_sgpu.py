@@ -218,3 +218,49 @@ def test_metax_sgpu_gpu_parity(seed, topo_default):
     assert all("metax-tech.com/gpu-devices-allocated" in r["annotations"] for r in fits)
     e.close()
     o.close()
+
+
+# ---- registration ----------------------------------------------------------------------------------------------------
+def test_get_node_devices_from_the_node_annotation():
+    # sdevice_test.go:507-590 (TestGetMetaxSDevices) + convertMetaxSDeviceToHAMIDevice (protocol.go:96-116)
+    import k8s_vgpu_scheduler_b200.engine as eng
+    anno = json.dumps([{"uuid": "GPU-123", "bdf": "0000:1a:00.0", "model": "MXC500", "totalDevCount": 16, "totalCompute": 100,
+                        "totalVRam": 32768, "availableDevCount": 16, "availableCompute": 100, "availableVRam": 32768,
+                        "numa": 1, "healthy": True, "qosPolicy": "fixed-share"},
+                       {"uuid": "GPU-456", "totalDevCount": 8, "totalCompute": 100, "totalVRam": 65536, "numa": 0, "healthy": False,
+                        "qosPolicy": "", "linkZone": 2}])
+    devs, pair = eng.decode_node_devices(SGPU, abi.HS_REG_METAX_SGPU, anno, None, "node-a")
+    assert pair is None
+    assert [(d["ID"], d["Index"], d["Count"], d["Devmem"], d["Devcore"], d["Type"], d["Numa"], d["Mode"], d["Health"], d["DeviceVendor"])
+            for d in devs] == [("GPU-123", 0, 16, 32768, 100, SGPU, 1, "", True, SGPU), ("GPU-456", 1, 8, 65536, 100, SGPU, 0, "", False, SGPU)]
+    assert [d["Sgpu"] for d in devs] == [{"qos_policy": "fixed-share", "link_zone": 0}, {"qos_policy": "", "link_zone": 2}]
+    for bad, msg in ((None, "annos not found metax-tech.com/node-gpu-devices"), ("", "unexpected end of JSON input"),
+                     ("[]", "no sdevice found on node"), ('{"uuid":"x"}', "cannot unmarshal object"),
+                     ('[{"uuid":"x","totalVRam":"big"}]', "MetaxSDeviceInfo.totalVRam of type int32")):
+        with pytest.raises(eng.IngestError) as ei:
+            eng.decode_node_devices(SGPU, abi.HS_REG_METAX_SGPU, bad, None, "n")
+        assert msg in str(ei.value), (bad, str(ei.value))
+
+
+@pytest.mark.gpu
+def test_sgpu_nodes_registered_from_the_annotation_decide_identically():
+    import parity
+    import k8s_vgpu_scheduler_b200.engine as eng
+    cfg, nodes, ops = sgpu_cluster(11, n_nodes=16, n_pods=400)
+    o = oa.Oracle(cfg["node_policy"], cfg["gpu_policy"], vendors=_vendors(False))
+    e = eng.Engine(cfg["node_policy"], cfg["gpu_policy"], vendors=_vendors(False))
+    for n in nodes:
+        o.node_upsert(n)
+        anno = json.dumps([{"uuid": d["id"], "totalDevCount": d["count"], "totalCompute": d["devcore"], "totalVRam": d["devmem"],
+                            "numa": d["numa"], "healthy": d["health"], "qosPolicy": d["sgpu"]["qos_policy"],
+                            "linkZone": d["sgpu"]["link_zone"]} for d in n["devices"]])
+        assert e.node_register(n["name"], [(SGPU, abi.HS_REG_METAX_SGPU, anno, None)]) == len(n["devices"]), e.error()
+    ref = [o.filter(arg) if kind == "filter" else {"status": o.pod_delete(arg)} for kind, arg in ops]
+    e.run_batch(eng.PackedOps(ops))
+    got = [e.batch_get(i) for i in range(len(ops))]
+    assert parity.compare(ops, ref, got) == []
+    for n in nodes:
+        assert e.snapshot_node_sgpu(n["name"]) == o.snapshot_node_sgpu(n["name"])
+    assert sum(r["status"] == abi.HS_FIT for r in ref) > 100
+    e.close()
+    o.close()

@@ -40,9 +40,9 @@ ASCEND_CORE = dict(word="Ascend910B3", kind=abi.HS_REQ_ASCEND, count="huawei.com
 
 
 def quantity(q):
-    """resource.Quantity as the three views the reference reads: (AsInt64 value, ok, Value() rounded up, Sign())."""
+    """resource.Quantity as the views the reference reads: (AsInt64 value, ok, Value() rounded up, Sign(), String() holds a letter)."""
     if isinstance(q, int):
-        return q, True, q, (q > 0) - (q < 0)
+        return q, True, q, (q > 0) - (q < 0), False
     s = q["_quantity"]
     m = re.match(r"^([+-]?)(\d+)(?:\.(\d+))?(m|k|M|G|T|Ki|Mi|Gi|Ti)?$", s)
     assert m, s
@@ -57,7 +57,9 @@ def quantity(q):
         v = sign * int(round(float("%d.%s" % (whole, frac)) * SUFFIX[suf]))
         return 0, False, v, (v > 0) - (v < 0)
     v = sign * whole * SUFFIX[suf]
-    return v, True, v, (v > 0) - (v < 0)
+    # the canonical String(): a binary-format quantity keeps a binary suffix from 1024 up, a decimal one gains k/M/G per factor of 1000
+    lettered = (abs(v) >= 1024 and v % 1024 == 0) if suf.endswith("i") else (v != 0 and v % 1000 == 0)
+    return v, True, v, (v > 0) - (v < 0), lettered
 
 
 def oracle_generate(v, limits, requests):
@@ -79,6 +81,25 @@ def oracle_generate(v, limits, requests):
             return None
         return {"Nums": 1, "Type": v["word"], "Memreq": wrap(mem[2]) if mem is not None else 0, "MemPercentagereq": -1,
                 "Coresreq": wrap(core[2]) if core is not None else 0}
+    if v["kind"] == abi.HS_REQ_METAX_SGPU:       # metax/sdevice.go:222-293: Limits only, vmemory in Gi unless it carries a unit
+        cnt, mem, core = limits.get(v["count"]), limits.get(v["mem"]), limits.get(v["cores"])
+        if cnt is None or not cnt[1] or cnt[0] <= 0 or cnt[0] > MAXI32:
+            return None
+        cores, memnum = 100, 0
+        if core is not None and core[1]:
+            if core[0] < 0 or core[0] > MAXI32:
+                return None
+            cores = core[0]
+        if mem is not None and mem[1]:
+            if mem[4]:
+                memnum = mem[0] // 1024 // 1024 if mem[0] >= 0 else -(-mem[0] // 1024 // 1024)
+            else:
+                if mem[0] < 0 or mem[0] > MAXI32 // 1024:
+                    return None
+                memnum = mem[0] * 1024
+            if memnum < 0 or memnum > MAXI32:
+                return None
+        return {"Nums": cnt[0], "Type": v["word"], "Memreq": memnum, "MemPercentagereq": 100 if memnum == 0 else 0, "Coresreq": cores}
     if v["kind"] == abi.HS_REQ_NEURON:           # awsneuron/device.go:287-334 (+ :115-154)
         def valid(q, maxv):
             return q[1] and 0 < q[0] <= maxv
@@ -238,14 +259,14 @@ def product_generate(vendors, limits, requests):
 
 
 def resources(case):
-    ctr = case.get("ctr") or case.get("args") or {}
+    ctr = case.get("ctr") or case.get("args") or case.get("container") or {}
     res = ctr.get("Resources", {}) if isinstance(ctr, dict) else {}
     conv = lambda d: {k: quantity(q) for k, q in d.items()} if isinstance(d, dict) else {}   # noqa: E731
     return conv(res.get("Limits", {})), conv(res.get("Requests", {}))
 
 
 def want_of(case):
-    w = case["want"]
+    w = case["want"] if "want" in case else case["expected"]
     if not isinstance(w, dict) or w.get("Nums", 0) <= 0:
         return None
     return {k: w.get(k, 0) for k in ("Nums", "Memreq", "MemPercentagereq", "Coresreq")} | {"Type": w["Type"]}
@@ -269,6 +290,7 @@ METAX = _plain("Metax-GPU", abi.HS_REQ_METAX, "metax-tech.com/gpu")
 # the golden table keeps the Go identifiers of the two resource names as its map keys (vdevice_test.go:430,444-445)
 XPU = _plain("XPU", abi.HS_REQ_KUNLUN_VXPU, "KunlunResourceVCount", "KunlunResourceVMemory")
 ENFLAME = _plain("Enflame", abi.HS_REQ_ENFLAME, "enflame.com/drs-gcu", "enflame.com/gcu-memory", "enflame.com/gcu-core")
+SGPU = _plain("Metax-SGPU", abi.HS_REQ_METAX_SGPU, "metax-tech.com/sgpu", "metax-tech.com/vmemory", "metax-tech.com/vcore")
 NEURON = dict(_plain("AWSNeuron", abi.HS_REQ_NEURON, "aws.amazon.com/neuron", None, "aws.amazon.com/neuroncore"), default_cores=2)
 
 TABLES = [("nvidia_generate_requests", NVIDIA, 15), ("hygon_generate_requests", DCU, 5), ("hygon_generate_requests_range", DCU, 2),
@@ -276,7 +298,8 @@ TABLES = [("nvidia_generate_requests", NVIDIA, 15), ("hygon_generate_requests", 
           ("ascend_generate_requests_range", ASCEND_CORE, 7),
           ("iluvatar_generate_requests", ILUVATAR, 5), ("biren_generate_requests", BIREN, 4), ("vastai_generate_requests", VASTAI, 4),
           ("mthreads_generate_requests", MTHREADS, 8), ("gcu_generate_requests", GCU, 3), ("metax_generate_requests", METAX, 2),
-          ("awsneuron_generate_requests", NEURON, 8), ("kunlun_vxpu_generate_requests", XPU, 3)]
+          ("awsneuron_generate_requests", NEURON, 8), ("kunlun_vxpu_generate_requests", XPU, 3),
+          ("metax_sgpu_generate_requests", SGPU, 10)]
 
 
 @pytest.mark.parametrize("name,vendor,count", TABLES, ids=[t[0] for t in TABLES])
@@ -372,3 +395,17 @@ def test_product_matches_restatement_on_random_containers():
         assert got == want, (limits, requests)
         kept += len(want)
     assert kept > 2000
+
+
+def test_metax_sgpu_vmemory_unit_rule():
+    # metax/sdevice.go:259-281: "has a unit" is read off Quantity.String(), whose canonical form turns 16000 into "16k"
+    sg = lambda **kw: {"metax-tech.com/sgpu": quantity(1)} | {"metax-tech.com/" + k: quantity({"_quantity": v}) for k, v in kw.items()}   # noqa: E731
+    for lim, want in ((sg(vmemory="16000"), (0, 100)), (sg(vmemory="16001"), (16001 * 1024, 0)), (sg(vmemory="2Gi"), (2048, 0)),
+                      (sg(vmemory="512Ki"), (0, 100)), (sg(vmemory="3M"), (2, 0)), (sg(vmemory="0"), (0, 100))):
+        ref = oracle_generate(SGPU, lim, {})
+        got = product_generate([SGPU], lim, {})
+        assert (ref["Memreq"], ref["MemPercentagereq"]) == want, lim
+        assert strip(got[0]) == strip(ref), lim
+    # Requests are not read at all (Limits only), and a lettered negative quantity lands below zero: the zero request
+    assert product_generate([SGPU], {}, {"metax-tech.com/sgpu": quantity(1)}) == []
+    assert product_generate([SGPU], sg(vmemory="-4Gi"), {}) == []
