@@ -360,6 +360,20 @@ __device__ __forceinline__ void stamp_decision(DevDecision& dec) {
 // GENERAL = false compiles the loop without the general evaluator (hs_eval.cuh): the host launches that instantiation
 // for ranges of ops that are all common-shape Filters and releases — fewer registers, no local-memory frame, and
 // more co-resident CTAs, i.e. a larger register-resident inventory.
+// The full evaluation of a warp's candidate nodes while the barrier is in flight (whole warp: fast_fit is a collective).
+// Resident mode: the group's own node, already in D.  Streaming mode: each group's best node of the sweep, loaded again
+// (nothing commits between the sweep and the barrier, so the copy is current); D and my_flags are scratch there.
+__device__ __forceinline__ void deferred_eval(const KernelArgs& ka, bool resident, int gg, int my_node, int glane,
+                                              uint32_t& my_flags, DevRegs& D, const DevPod& pod, FastEval& fe) {
+  int node = gg;
+  if (!resident) {
+    node = my_node >= 0 ? my_node : 0;
+    my_flags = ka.node_flags[node];
+    load_dev(ka, node, glane, D);
+  }
+  fast_fit(D, glane, (uint32_t)node, my_flags, pod, pod.e0, ka, fe);
+}
+
 template <bool GENERAL>
 __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
   __shared__ __align__(16) DevPod s_op[HS_PF];
@@ -517,14 +531,13 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
       if (gtid == 0) { ka.decisions[r].status = -1; ka.decisions[r].node = -1; ka.decisions[r].n_alloc = 0; }
       continue;
     }
-    // streaming mode only: in resident mode the full evaluation runs in parallel everywhere, so the winner can
-    // commit straight after the barrier (measured: deferring it to the winner lengthens the critical path)
-    // Without numa-bind the VERDICT needs no score/sort (fast_fit_lite).  Streaming mode: the winner's warp runs the
-    // full evaluation afterwards.  Resident mode: every group that fits runs it while the barrier's
-    // arrivals (and, across GPUs, the mailbox round trip) are in flight (`deferred`), so the winner still commits
-    // straight after the barrier.
+    // Without numa-bind the VERDICT needs no score/sort (fast_fit_lite).  The full evaluation that tells WHICH devices
+    // runs while the barrier's arrivals (and, across GPUs, the mailbox round trip) are in flight (`deferred`), in the
+    // warp that holds its CTA's best key — on the register-resident node, or in streaming mode on that warp's best
+    // nodes loaded again — so the winner commits straight after the barrier.
     const bool lite = fast && !hs_verdict_needs_order(pod);
-    const bool deferred = lite && resident;
+    const bool deferred = lite;
+    bool evaluated = false;      // warp-uniform: this warp ran the deferred evaluation of its groups' best nodes
     const DevEntry* ent = &pod.e0;
     if (pod.n_entries > 1) {     // general path with several entries: fetch them from the pool
       const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.entries + pod.entry_off);
@@ -643,8 +656,10 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
       }
       // Only the warp that holds the CTA's best key can hold the winner: the others skip the full evaluation and
       // leave the issue slots to it (s_red holds every warp's key since slot_arrive's __syncthreads).
-      if (deferred && bk != 0ull && bk == cta_best(s_red))  // warp-uniform: fast_fit is a whole-warp collective
-        fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
+      if (deferred && bk != 0ull && bk == cta_best(s_red)) {  // warp-uniform: fast_fit is a whole-warp collective
+        evaluated = true;
+        deferred_eval(ka, resident, gg, my_node, glane, my_flags, D, pod, fe);
+      }
       // (choosing the devices here too, in every group that fits, was measured 8 % SLOWER than leaving fast_pick to
       // the one winner: 5 000 groups pay for it, one benefits)
       win = slot_wait(ka.sync + r, &s_win);
@@ -655,7 +670,10 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
       }
     } else if (deferred) {
       xgpu_arrive(ka, ka.sync + r, barriers, bk, s_red);
-      if (bk != 0ull && bk == cta_best(s_red)) fast_fit(D, glane, (uint32_t)gg, my_flags, pod, pod.e0, ka, fe);
+      if (bk != 0ull && bk == cta_best(s_red)) {
+        evaluated = true;
+        deferred_eval(ka, resident, gg, my_node, glane, my_flags, D, pod, fe);
+      }
       win = xgpu_wait(ka, barriers, &s_win);
     } else {
       win = slot_argbest(ka, ka.sync + r, barriers, bk, s_red, &s_win);
@@ -679,7 +697,7 @@ __device__ __forceinline__ void decide_loop(const KernelArgs& ka) {
         }
       }
       if (fast) {
-        if (!resident && __any_sync(FULL, mine)) {
+        if (!resident && !evaluated && __any_sync(FULL, mine)) {
           // the sweep only established THAT the node fits (or ran on streamed registers): the winner's warp
           // now runs the full evaluation to learn which devices (collectives → the whole warp takes part)
           if (!resident) {
