@@ -347,7 +347,10 @@ def scan_probe(n_nodes, peak):
     out = {"kernel": "hs_sweep_kernel", "nodes": n_nodes, "peak": peak, "unit": "GB/s"}
     try:
         for key, flag in (("idle", []), ("realistic", ["--realistic"])):
-            lines = subprocess.run([exe] + flag + [str(n_nodes)], capture_output=True, text=True, timeout=600).stdout.strip().splitlines()
+            proc = subprocess.run([exe] + flag + [str(n_nodes)], capture_output=True, text=True, timeout=600)
+            if proc.returncode != 0 or not proc.stdout.strip():
+                raise RuntimeError("hs_scan_probe %s exited %d: %s" % (" ".join(flag), proc.returncode, proc.stderr.strip()[-200:]))
+            lines = proc.stdout.strip().splitlines()
             rows = [json.loads(x) for x in lines]
             out[key] = [{"request": r["request"], "ms": r["ms"], "achieved": r["algorithmic_gbps"],
                          "frac": round(r["algorithmic_gbps"] / peak, 4), "fits": r["fits"]} for r in rows]

@@ -45,6 +45,7 @@ int main(int argc, char** argv) {
     g_rng = 0x9E3779B97F4A7C15ull;
     for (long i = 0; i < n; i++) {
       hs_device_info d[8];
+      memset(d, 0, sizeof d);          // the optional parts (MIG profiles, vendor CustomInfo) stay absent
       const unsigned kind = realistic ? rnd() % 100 : 0;     // <50 NVIDIA, <70 Ascend, <85 MLU, else DCU
       const int model = (int)(rnd() % 4);
       for (int k = 0; k < 8; k++) {
