@@ -919,6 +919,7 @@ hs_sweep_kernel(const KernelArgs ka, int op) {
     constexpr bool lite = MODE == 2;
     DevRegs n;
     FastEval fe;
+    const LiteReq lq = lite_req(pod, pod.e0);   // the request's invariants, in registers for the whole walk
     // software pipeline: the next node's three loads are in flight while this node is evaluated
     int node = gg;
     int4 nt = make_int4(0, 0, 0, 0), a = nt, b = nt;
@@ -939,7 +940,7 @@ hs_sweep_kernel(const KernelArgs ka, int op) {
       const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
       n.used = a.x; n.mem = a.y; n.cores = a.z; n.dflags = (uint32_t)a.w;
       n.count = b.x; n.totmem = b.y; n.totcore = b.z; n.packed = (uint32_t)b.w;
-      const bool fit = (lite ? fast_fit_lite(n, glane, gbase, (uint32_t)node, nf, pod, pod.e0, ka)
+      const bool fit = (lite ? fast_fit_lite_q(n, glane, gbase, (uint32_t)node, nf, lq, pod.e0, ka)
                              : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, fe)) && pos >= 0;
       float term = 0.0f;
       if (!lite && hs_is_net_scored(pod)) { int row_; fast_ascend_select(n, glane, gbase, fit, pod.e0, fe, &row_, &term); }
@@ -967,6 +968,111 @@ hs_sweep_kernel(const KernelArgs ka, int op) {
         my_key = key > my_key ? key : my_key;
       }
     }
+  }
+  unsigned long long bk = warp_max_u64(my_key);
+  if (lane == 0) s_red[threadIdx.x >> 5] = bk;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int i = 1; i < (int)(blockDim.x >> 5); i++) bk = s_red[i] > bk ? s_red[i] : bk;
+    if (bk) atomicMax(&ka.sync[op].best, bk);
+  }
+}
+
+// ---- the same scan with the inventory staged through shared memory by the TMA (cp.async.bulk) ----------------------
+// A CTA's 32 node groups walk 32 CONSECUTIVE nodes per step, i.e. one contiguous 4 KiB run of `dyn`, one of `stat` and
+// 512 B of `node_tot`: three bulk copies into a ring of SW_ST stages, completion counted on one mbarrier per stage.  The
+// loads of the next SW_ST - 1 steps are in flight while a step is evaluated, and they cost no registers — the register
+// pipeline above holds ONE step ahead, which leaves the scan short of bytes in flight.  Only this GPU's own
+// memory is read, and no copy is multicast.
+constexpr int SW_ST = 4;
+struct __align__(128) SweepStage { int4 dyn[256]; int4 stat[256]; int4 tot[32]; };
+static_assert(sizeof(SweepStage) == 8704, "stage layout");
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* b, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* b, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* b, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "SW_WAIT:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra SW_DONE;\n\t"
+      "bra SW_WAIT;\n\t"
+      "SW_DONE:\n\t"
+      "}" ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* b) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(b)) : "memory");
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256, (MODE == 1 ? 4 : 5))
+hs_sweep_tma_kernel(const KernelArgs ka, int op) {
+  static_assert(MODE == 1 || MODE == 2, "lane-per-device modes only");
+  __shared__ SweepStage ring[SW_ST];
+  __shared__ __align__(8) unsigned long long full[SW_ST];
+  __shared__ __align__(16) DevPod s_pod;
+  __shared__ unsigned long long s_red[8];
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(ka.pods + op);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&s_pod);
+    for (int i = threadIdx.x; i < (int)(sizeof(DevPod) / 4); i += blockDim.x) dst[i] = src[i];
+  }
+  if (threadIdx.x == 0) {
+    for (int s_ = 0; s_ < SW_ST; s_++) mbar_init(&full[s_], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const DevPod& pod = s_pod;
+  const int lane = threadIdx.x & 31;
+  const int glane = lane & 7, gbase = lane & 24;
+  const bool spread = pod.flags & PF_NODE_SPREAD;
+  const int tile0 = (int)blockIdx.x * 32, tstride = (int)gridDim.x * 32;        // n_nodes % 32 == 0: whole tiles only
+  const int T = tile0 < ka.n_nodes ? (ka.n_nodes - tile0 + tstride - 1) / tstride : 0;
+  auto issue = [&](int k) {
+    SweepStage& st = ring[k % SW_ST];
+    unsigned long long* b = &full[k % SW_ST];
+    const size_t node0 = (size_t)tile0 + (size_t)k * tstride;
+    mbar_expect_tx(b, (uint32_t)sizeof(SweepStage));
+    bulk_g2s(st.dyn, ka.dyn + node0 * HS_D, sizeof st.dyn, b);
+    bulk_g2s(st.stat, ka.stat + node0 * HS_D, sizeof st.stat, b);
+    bulk_g2s(st.tot, ka.node_tot + node0, sizeof st.tot, b);
+  };
+  if (threadIdx.x == 0)
+    for (int k = 0; k < T && k < SW_ST; k++) issue(k);
+  constexpr bool lite = MODE == 2;
+  const LiteReq lq = lite_req(pod, pod.e0);
+  unsigned long long my_key = 0;
+  DevRegs n;
+  FastEval fe;
+  // (Measured and not kept: per-stage "empty" mbarriers instead of the CTA barrier below, the walk unrolled over the ring —
+  // 0.62 of peak against 0.68; the producer thread's wait stalls its whole warp and the spinning costs issue slots.)
+  for (int k = 0; k < T; k++) {
+    const SweepStage& st = ring[k % SW_ST];
+    mbar_wait(&full[k % SW_ST], (uint32_t)(k / SW_ST) & 1u);
+    const int4 a = st.dyn[threadIdx.x], b = st.stat[threadIdx.x], nt = st.tot[threadIdx.x >> 3];
+    const int node = tile0 + k * tstride + (int)(threadIdx.x >> 3);
+    const uint32_t nf = (uint32_t)nt.x;
+    const int pos = (nf & NF_ALIVE) ? (ka.cand_pos ? ka.cand_pos[node] : node) : -1;
+    n.used = a.x; n.mem = a.y; n.cores = a.z; n.dflags = (uint32_t)a.w;
+    n.count = b.x; n.totmem = b.y; n.totcore = b.z; n.packed = (uint32_t)b.w;
+    const bool fit = (lite ? fast_fit_lite_q(n, glane, gbase, (uint32_t)node, nf, lq, pod.e0, ka)
+                           : fast_fit(n, glane, (uint32_t)node, nf, pod, pod.e0, ka, fe)) && pos >= 0;
+    float term = 0.0f;
+    if (!lite && hs_is_net_scored(pod)) { int row_; fast_ascend_select(n, glane, gbase, fit, pod.e0, fe, &row_, &term); }
+    if (fit) {
+      const float sc = __fadd_rn(__int_as_float(nt.y), term);
+      const unsigned long long key = make_key(sc, spread, (uint32_t)(ka.pos_base + pos));
+      my_key = key > my_key ? key : my_key;
+    }
+    __syncthreads();                       // every thread has read stage k % SW_ST: it can be filled again
+    if (threadIdx.x == 0 && k + SW_ST < T) issue(k + SW_ST);
   }
   unsigned long long bk = warp_max_u64(my_key);
   if (lane == 0) s_red[threadIdx.x >> 5] = bk;
@@ -1174,7 +1280,22 @@ extern "C" int hs_decide_max_blocks(int block, int device, int fast_only) {
   return per_sm * sms;
 }
 // mode: 0 general, 1 lane-per-device full, 2 lane-per-device order-free (see hs_sweep_kernel)
+static int sweep_tma_enabled() {      // HS_SWEEP_TMA=0 keeps the register-pipelined scan (A/B measurements)
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("HS_SWEEP_TMA");
+    v = (e && e[0] == '0') ? 0 : 1;
+    cudaFuncSetAttribute(hs_sweep_tma_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    cudaFuncSetAttribute(hs_sweep_tma_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  }
+  return v;
+}
 extern "C" int hs_launch_sweep(const KernelArgs* ka, int op, int mode, int grid, int block, cudaStream_t stream) {
+  if (mode != 0 && block == 256 && sweep_tma_enabled()) {
+    if (mode == 2) hs_sweep_tma_kernel<2><<<grid, block, 0, stream>>>(*ka, op);
+    else hs_sweep_tma_kernel<1><<<grid, block, 0, stream>>>(*ka, op);
+    return (int)cudaGetLastError();
+  }
   if (mode == 2) hs_sweep_kernel<2><<<grid, block, 0, stream>>>(*ka, op);
   else if (mode == 1) hs_sweep_kernel<1><<<grid, block, 0, stream>>>(*ka, op);
   else hs_sweep_kernel<0><<<grid, block, 0, stream>>>(*ka, op);
