@@ -344,7 +344,8 @@ def scan_probe(n_nodes, peak):
     vendor / type mix, ~70 % of the devices in use, 2 % unhealthy; requests with a type selector, a UUID list, numa-bind).
     algorithmic bytes = nodes x 8 x 32 B."""
     exe = os.path.join(ROOT, "k8s-vgpu-scheduler_b200", "hs_scan_probe")
-    out = {"kernel": "hs_sweep_kernel", "nodes": n_nodes, "peak": peak, "unit": "GB/s"}
+    tma = os.environ.get("HS_SWEEP_TMA", "1")[:1] != "0"      # the library's default: inventory staged by cp.async.bulk
+    out = {"kernel": "hs_sweep_tma_kernel" if tma else "hs_sweep_kernel", "nodes": n_nodes, "peak": peak, "unit": "GB/s"}
     try:
         for key, flag in (("idle", []), ("realistic", ["--realistic"])):
             proc = subprocess.run([exe] + flag + [str(n_nodes)], capture_output=True, text=True, timeout=600)

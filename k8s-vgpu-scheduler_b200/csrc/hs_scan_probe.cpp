@@ -119,9 +119,11 @@ int main(int argc, char** argv) {
       if (rc < 0) { fprintf(stderr, "probe: %s\n", hs_last_error(h)); return 1; }
       const double nodes_padded = (double)((n + 31) / 32 * 32);
       const double bytes = nodes_padded * 256.0;              // N x 8 x 32 B
-      printf("{\"kernel\": \"hs_sweep_kernel\", \"inventory\": \"%s\", \"nodes\": %ld, \"request\": \"%s\", \"inventory_mb\": %.2f, \"ms\": %.5f, "
+      const char* tma_env = getenv("HS_SWEEP_TMA");
+      const char* kname = (tma_env && tma_env[0] == '0') ? "hs_sweep_kernel" : "hs_sweep_tma_kernel";
+      printf("{\"kernel\": \"%s\", \"inventory\": \"%s\", \"nodes\": %ld, \"request\": \"%s\", \"inventory_mb\": %.2f, \"ms\": %.5f, "
              "\"algorithmic_gbps\": %.1f, \"with_node_records_gbps\": %.1f, \"winner\": %d, \"fits\": %s, \"iters\": %u, \"devices_in_use\": %ld, \"unhealthy\": %ld}\n",
-             realistic ? "realistic (C4 mix, ~70% in use, 2% unhealthy)" : "idle homogeneous B200", n, sh.what, bytes / 1e6, ms,
+             kname, realistic ? "realistic (C4 mix, ~70% in use, 2% unhealthy)" : "idle homogeneous B200", n, sh.what, bytes / 1e6, ms,
              bytes / (ms * 1e-3) / 1e9, nodes_padded * 272.0 / (ms * 1e-3) / 1e9, idx, rc == 0 ? "true" : "false", iters, used_devices, unhealthy);
       fflush(stdout);
     }
