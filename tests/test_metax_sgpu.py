@@ -264,3 +264,105 @@ def test_sgpu_nodes_registered_from_the_annotation_decide_identically():
     assert sum(r["status"] == abi.HS_FIT for r in ref) > 100
     e.close()
     o.close()
+
+
+# ---- the in-flight QoS switch cache (JitteryQosCache), replayed through the oracle's Filter / register flow -----------
+def _qos_node(policies):
+    return {"name": "mx-q", "devices": [
+        {"id": uid, "index": i, "count": 16, "devmem": 32768, "devcore": 100, "type": SGPU, "numa": 0, "mode": "", "health": True,
+         "vendor": SGPU, "sgpu": {"qos_policy": pol, "link_zone": 0}} for i, (uid, pol) in enumerate(policies)]}
+
+
+def _qos_pod(uid, qos, card, cores):
+    return {"uid": uid, "ns": "default", "name": uid, "annotations": {QOS: qos, "metax-tech.com/use-gpuuuid": card},
+            "containers": [[{"key": SGPU, "type": SGPU, "nums": card.count(",") + 1, "memreq": 1024, "mempct": 0, "coresreq": cores}]]}
+
+
+def _pending(o):
+    return {uid: p for uid, (_, _, p) in zip(("GPU-123", "GPU-456", "GPU-789"), o.snapshot_node_sgpu("mx-q")) if p is not None}
+
+
+def test_add_jittery_qos_vector():
+    # sdevice_test.go:680-737 (TestAddJitteryQos): a best-effort pod on GPU-123 (best-effort) and GPU-456 (burst-share) at 50
+    # cores, and on GPU-789 (best-effort) at 100 cores -> {GPU-456: best-effort, GPU-789: ""}; the device that already runs the
+    # pod's policy gets no entry, a whole card is expected to drop its policy
+    o = oa.Oracle()
+    o.node_upsert(_qos_node([("GPU-123", "best-effort"), ("GPU-456", "burst-share"), ("GPU-789", "best-effort")]))
+    assert o.filter(_qos_pod("p1", "best-effort", "GPU-123,GPU-456", 50))["status"] == abi.HS_FIT
+    assert _pending(o) == {"GPU-456": "best-effort"}
+    assert o.filter(_qos_pod("p2", "best-effort", "GPU-789", 100))["status"] == abi.HS_FIT
+    assert _pending(o) == {"GPU-456": "best-effort", "GPU-789": ""}
+    o.close()
+
+
+@pytest.mark.parametrize("first,placed,want", [
+    # qos_test.go:24-120 (TestJitteryQosCacheSync): every device reports best-effort at the sync
+    (("burst-share", "best-effort"), ("fixed-share", "burst-share"), {"GPU-123": "fixed-share", "GPU-789": "burst-share"}),   # "no sync"
+    (("fixed-share", "best-effort"), ("best-effort", "burst-share"), {"GPU-789": "burst-share"}),                             # one retired
+    (("fixed-share", "burst-share"), ("best-effort", "best-effort"), {}),                                                    # both retired
+], ids=["no-sync", "sync-one", "sync-both"])
+def test_jittery_qos_cache_sync_vectors(first, placed, want):
+    o = oa.Oracle()
+    o.node_upsert(_qos_node([("GPU-123", first[0]), ("GPU-456", "best-effort"), ("GPU-789", first[1])]))
+    assert o.filter(_qos_pod("a", placed[0], "GPU-123", 50))["status"] == abi.HS_FIT
+    assert o.filter(_qos_pod("b", placed[1], "GPU-789", 50))["status"] == abi.HS_FIT
+    assert _pending(o) == {"GPU-123": placed[0], "GPU-789": placed[1]}          # the currentCache of the reference's case
+    o.node_upsert(_qos_node([("GPU-123", "best-effort"), ("GPU-456", "best-effort"), ("GPU-789", "best-effort")]))   # Sync(devices)
+    assert _pending(o) == want
+    o.close()
+
+
+def test_check_device_qos_reads_the_pending_switch():
+    # sdevice.go:528-556 with a cache entry (JitteryQosCache.Get, qos_test.go:122-160): while GPU-123 is switching to fixed-share a
+    # second fixed-share pod shares it, a best-effort pod — the policy the device still REPORTS — is refused
+    o = oa.Oracle()
+    o.node_upsert(_qos_node([("GPU-123", "best-effort"), ("GPU-456", "best-effort"), ("GPU-789", "best-effort")]))
+    assert o.filter(_qos_pod("a", "fixed-share", "GPU-123", 30))["status"] == abi.HS_FIT
+    assert _pending(o) == {"GPU-123": "fixed-share"}
+    assert o.filter(_qos_pod("b", "fixed-share", "GPU-123", 30))["status"] == abi.HS_FIT
+    r = o.filter(_qos_pod("c", "best-effort", "GPU-123", 30))
+    assert r["status"] == abi.HS_NOFIT and "CardQosPolicyMismatch" in " ".join(r["failed"].values())
+    o.close()
+
+
+@pytest.mark.parametrize("node_policy", ["binpack", "spread"])
+def test_score_node_is_policy_neutral_through_filter(node_policy):
+    # sdevice_test.go:2947-3035 (TestScoreNodePolicyIndependence) at the level where it matters: the node that keeps its MetaLink
+    # zones whole wins the topology-aware pod under BOTH node policies (a policy-signed weight would flip the choice under one)
+    def node(name, zones):
+        return {"name": name, "devices": [
+            {"id": "%s-%d" % (name, i), "index": i, "count": 16, "devmem": 32768, "devcore": 100, "type": SGPU, "numa": 0, "mode": "",
+             "health": True, "vendor": SGPU, "sgpu": {"qos_policy": "", "link_zone": z}} for i, z in enumerate(zones)]}
+    pod = {"uid": "t", "ns": "default", "name": "t", "annotations": {TOPO: "true"},
+           "containers": [[{"key": SGPU, "type": SGPU, "nums": 2, "memreq": 0, "mempct": 100, "coresreq": 100}]]}
+    scores = {}
+    for order in (("whole", "split"), ("split", "whole")):          # the candidate order must not decide it either
+        o = oa.Oracle(node_policy, "binpack")
+        o.node_upsert(node("whole", [1, 1, 2, 2]))                  # taking one zone's two cards breaks no pair elsewhere
+        o.node_upsert(node("split", [1, 1, 1, 1]))                  # taking two of four breaks five of the six pairs
+        r = o.filter(pod, node_names=list(order))
+        assert r["status"] == abi.HS_FIT and r["node"] == "whole", (node_policy, order, r["node"], r["score"])
+        scores[order] = r["score"]
+        o.close()
+    assert len(set(scores.values())) == 1
+
+
+def test_allocated_annotation_is_metaxs_own_json():
+    # PatchAnnotations (sdevice.go:142-171) + convertHAMIPodDeviceToMetaxPodDevice (protocol.go:129-145; protocol_test.go:118-198):
+    # per container a list of {"uuid", "compute", "vRam"} with Go's omitempty on the two numbers, beside the two hami keys
+    o = oa.Oracle()
+    o.node_upsert(_qos_node([("GPU-123", ""), ("GPU-456", ""), ("GPU-789", "")]))
+    pod = {"uid": "j", "ns": "default", "name": "j", "annotations": {},
+           "containers": [[{"key": SGPU, "type": SGPU, "nums": 2, "memreq": 1024, "mempct": 0, "coresreq": 0}],
+                          [{"key": SGPU, "type": SGPU, "nums": 1, "memreq": 10240, "mempct": 0, "coresreq": 20}]]}
+    r = o.filter(pod)
+    assert r["status"] == abi.HS_FIT
+    ctrs = r["devices"][SGPU]
+    want = [[{"uuid": d[0]} | ({"compute": d[3]} if d[3] else {}) | ({"vRam": d[2]} if d[2] else {}) for d in c] for c in ctrs]
+    got = r["annotations"]["metax-tech.com/gpu-devices-allocated"]
+    assert got == json.dumps(want, separators=(",", ":"))
+    assert [len(c) for c in json.loads(got)] == [2, 1] and "compute" not in json.loads(got)[0][0] and json.loads(got)[1][0]["compute"] == 20
+    assert r["annotations"]["metax-tech.com/predicate-time"] == ""               # the caller stamps it
+    assert r["annotations"]["hami.io/metax-sgpu-devices-to-allocate"] == r["annotations"]["hami.io/metax-sgpu-devices-allocated"]
+    assert QOS not in r["annotations"]        # the "best-effort" default is the webhook's (MutateAdmission, :89-129), not Filter's
+    o.close()
