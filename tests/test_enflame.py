@@ -238,3 +238,20 @@ def test_enflame_nodes_registered_from_the_annotation_decide_identically():
     got = [e.batch_get(i) for i in range(len(ops))]
     e.close()
     assert parity.compare(ops, ref, got) == []
+
+
+def test_drs_capacity_parsing_vectors():
+    # device_test.go:420-437 (TestParseDRSCapacity_RejectsNaNAndInf) + parseDRSCapacity / clampToInt32 (device.go:643-675) as
+    # they show through GetNodeDevices: a JSON number is a float64 (refused above MaxInt32, truncated toward zero below), a
+    # string goes through Atoi after TrimSpace and is clamped, anything else — and a capacity that is not positive — is refused
+    import k8s_vgpu_scheduler_b200.engine as eng
+
+    def count(cap):
+        anno = '{"devices":[{"index":"0","minor":"0","capacity":%s}],"profiles":{"1g.6gb":"0"}}' % cap
+        try:
+            return eng.decode_node_devices("Enflame", abi.HS_REG_ENFLAME_DRS, anno, None, "n")[0][0]["Count"]
+        except eng.IngestError as e:
+            assert "invalid drs capacity on node n" in str(e)
+            return None
+    assert [count(c) for c in ("42", "42.0", "42.9", "2147483647.0", '"2147483648"', '" 7 "')] == [42, 42, 42, 2 ** 31 - 1, 2 ** 31 - 1, 7]
+    assert [count(c) for c in ("2147483648", "1e300", "3e9", '"7.5"', "-3", '"-9999999999"', "true", "null", "0")] == [None] * 9

@@ -277,3 +277,20 @@ def test_general_path_in_streaming_mode(monkeypatch):
     ref, ref_snap = parity.run_oracle(cfg, nodes, ops)
     got, snap = parity.run_engine(cfg, nodes, ops, chunk=125)
     assert parity.compare(ops, ref, got, ref_snap, snap) == []
+
+
+def test_vxpu_get_node_devices_vectors():
+    # vdevice_test.go:215-277 (Test_GetNodeDevices): missing annotation, invalid JSON, empty list, and a list whose devices
+    # take the vendor word; ascend words the empty list the same way (ascend/device.go:212), the others say "gpu"
+    import k8s_vgpu_scheduler_b200.engine as eng
+    for anno, msg in ((None, "annos not found"), ("not-json", "invalid"), ("[]", "no device found on node")):
+        with pytest.raises(eng.IngestError) as ei:
+            eng.decode_node_devices("XPU", abi.HS_REG_JSON, anno, None, "n")
+        assert msg in str(ei.value)
+    devs, _ = eng.decode_node_devices("XPU", abi.HS_REG_JSON,
+                                      '[{"id":"xpu-0","index":0,"count":1,"devmem":98304,"devcore":100,"type":"XPU","health":true}]', None, "n")
+    assert [(d["ID"], d["DeviceVendor"], d["Type"], d["Devmem"], d["Health"]) for d in devs] == [("xpu-0", "XPU", "XPU", 98304, True)]
+    for vendor, msg in (("Ascend910B3", "no device found on node"), ("NVIDIA", "no gpu found on node"), ("Iluvatar", "no gpu found on node")):
+        with pytest.raises(eng.IngestError) as ei:
+            eng.decode_node_devices(vendor, abi.HS_REG_JSON, "[]", None, "n")
+        assert msg in str(ei.value)
