@@ -524,7 +524,9 @@ int32_t hs_generate_requests(const hs_vendor_resources* vendors, uint32_t n_vend
  * The reference learns a node's devices from register annotations and a pod's committed allocation from its
  * "<vendor>-devices-allocated" annotations; these entry points take the annotation STRINGS.                */
 enum { HS_REG_CSV = 0,    /* device.DecodeNodeDevices  (pkg/device/devices.go:317-381): DCU, iluvatar      */
-       HS_REG_JSON = 1,   /* device.UnMarshalNodeDevices (pkg/device/devices.go:445-449): NVIDIA, Ascend, … */
+       HS_REG_JSON = 1,   /* device.UnMarshalNodeDevices (pkg/device/devices.go:445-449): NVIDIA, Ascend, …;
+                           * for both annotation formats capacity_cores > 0 overwrites every device's Devcore, which is
+                           * what biren/device.go:84 and vastai/device.go:86 do with 100 after the decode              */
        /* no annotation at all: the devices are derived from the node's CAPACITY (capacity_cores / capacity_memory =
         * AsInt64 of Status.Capacity[<cores resource>] / [<memory resource>]) and named after the node:               */
        HS_REG_CAPACITY_MLU = 2,      /* cambricon/device.go:209-232: one card per 100 cores, <node>-cambricon-mlu-<i>   */
@@ -534,6 +536,8 @@ enum { HS_REG_CSV = 0,    /* device.DecodeNodeDevices  (pkg/device/devices.go:31
                                       * .scores values or NULL (hs_node_register hands them to hs_node_info)            */
        HS_REG_CAPACITY_KUNLUN = 6,   /* kunlun/device.go:64-91: capacity_cores = the XPU count, <node>-kunlun-<i>, Count 100,
                                       * 98304 MiB, the upper half of the cards on NUMA 1                                */
+       HS_REG_CAPACITY_GCU = 9,      /* enflame/gcu.go:67-89: capacity_cores = the node's enflame.com/gcu count, <node>-GCU-<i>,
+                                      * whole cards: Count 1, Devmem 100, Devcore 100                                    */
        HS_REG_METAX_SGPU = 8,        /* metax/sdevice.go:506-526 + protocol.go:96-116: `annotation` = the node's
                                       * metax-tech.com/node-gpu-devices JSON ([]MetaxSDeviceInfo); Index = position             */
        HS_REG_ENFLAME_DRS = 7,       /* enflame/device.go:198-252: `annotation` = the node's enflame.com/gcu-drs-capacity JSON

@@ -123,7 +123,7 @@ class hs_sim_node(C.Structure):
 
 
 HS_REG_CSV, HS_REG_JSON, HS_REG_CAPACITY_MLU, HS_REG_CAPACITY_MTHREADS, HS_REG_CAPACITY_METAX, HS_REG_CAPACITY_NEURON = 0, 1, 2, 3, 4, 5
-HS_REG_CAPACITY_KUNLUN, HS_REG_ENFLAME_DRS, HS_REG_METAX_SGPU = 6, 7, 8
+HS_REG_CAPACITY_KUNLUN, HS_REG_ENFLAME_DRS, HS_REG_METAX_SGPU, HS_REG_CAPACITY_GCU = 6, 7, 8, 9
 
 
 class hs_container_request(C.Structure):

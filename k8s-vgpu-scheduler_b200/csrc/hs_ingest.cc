@@ -677,6 +677,18 @@ bool devices_from_capacity(int kind, const std::string& node, int64_t cores, int
     }
     return true;
   }
+  if (kind == 4) {                                         // enflame/gcu.go:67-89: `cores` carries the GCU count; whole cards, 100 / 100
+    if (cores == 0) { err = "device not found enflame.com/gcu"; return false; }
+    for (int64_t i = 0; i < cores; i++) {
+      Device d;
+      d.index = (uint32_t)i;
+      d.id = node + "-GCU-" + std::to_string(i);
+      d.count = 1; d.devmem = 100; d.devcore = 100; d.type = "GCU"; d.numa = 0; d.health = true;
+      out.push_back(d);
+      if (out.size() > 4096) { err = "capacity yields more than 4096 cards"; out.clear(); return false; }
+    }
+    return true;
+  }
   if (kind == 2) {                                         // metax/device.go:67-89: `cores` carries the GPU count
     if (cores == 0) { err = "device not found metax-tech.com/gpu"; return false; }
     for (int64_t i = 0; i < cores; i++) {

@@ -435,3 +435,50 @@ def test_decode_mig_allocations_golden():
         {"containerIndex":0,"deviceIndex":1,"gpuUUID":"GPU-a","profile":"1g.5gb","placement":{"start":5,"size":1}}
     ]'''
     assert eng.decode_mig_allocations(two) == [("GPU-a", "1g.5gb", 6, 1), ("GPU-a", "1g.5gb", 5, 1)]
+
+
+def test_hygon_and_ascend_get_node_devices_vectors():
+    # hygon/device_test.go:242-330 and ascend/device_test.go:168-262 (Test_GetNodeDevices): the rows those tests compare, the
+    # error returns with the texts of the code they reach (devices.go:317-384 DecodeNodeDevices, ascend/device.go:197-215)
+    def run(vendor, fmt, anno):
+        devs, _ = eng.decode_node_devices(vendor, fmt, anno, None, "n")
+        return [(d["ID"], d["Index"], d["Count"], d["Devmem"], d["Devcore"], d["Type"], d["Numa"], d["Health"], d["Mode"], d["DeviceVendor"]) for d in devs]
+    assert run("DCU", abi.HS_REG_CSV, "test-0,1,1024,100,DCU,0,true,0,test:") == [("test-0", 0, 1, 1024, 100, "DCU", 0, True, "test", "DCU")]
+    for anno, msg in ((None, "annos not found"), (":", "no gpu found on node"), ("", "node annotation missing device separator"),
+                      ("test-0,1,1024,100,DCU:", "unexpected field count 5")):
+        with pytest.raises(eng.IngestError) as ei:
+            run("DCU", abi.HS_REG_CSV, anno)
+        assert msg in str(ei.value), (anno, str(ei.value))
+    anno = '[{"ID":"GPU-0","Count":4,"Devmem":8738,"Devcore":8,"Type":"huawei.com/Ascend910","Numa":0,"Health":true}]'
+    assert run("Ascend910A", abi.HS_REG_JSON, anno) == [("GPU-0", 0, 4, 8738, 8, "huawei.com/Ascend910", 0, True, "", "Ascend910A")]
+    for anno, msg in (("[]", "no device found on node"), (None, "annos not found"), ("", "unexpected end of JSON input")):
+        with pytest.raises(eng.IngestError) as ei:
+            run("Ascend910A", abi.HS_REG_JSON, anno)
+        assert msg in str(ei.value), (anno, str(ei.value))
+
+
+def test_plain_vendor_get_node_devices_vectors():
+    # Test_GetNodeDevices of iluvatar (device_test.go:35-133), amd (:149-170), biren (:83-160), vastai (:83-160) and
+    # TestGCUDevices_GetNodeDevices (enflame/gcu_test.go:194-300), through the product's decoder
+    def run(vendor, fmt, anno, **kw):
+        devs, _ = eng.decode_node_devices(vendor, fmt, anno, None, kw.pop("node", "n"), **kw)
+        return [(d["ID"], d["Index"], d["Count"], d["Devmem"], d["Devcore"], d["Type"], d["Numa"], d["Health"], d["Mode"], d["DeviceVendor"]) for d in devs]
+    assert run("MR-V100", abi.HS_REG_CSV, "GPU-bad51c5a-ed4c-591d-91bf-c04a12e19eae,10,8192,100,MR-V100,0,true:") == [
+        ("GPU-bad51c5a-ed4c-591d-91bf-c04a12e19eae", 0, 10, 8192, 100, "MR-V100", 0, True, "hami-core", "MR-V100")]
+    assert run("AMD", abi.HS_REG_JSON, '[{"id":"GPU-0","index":0,"count":1,"devmem":8192,"devcore":100,"type":"amd","numa":0,"health":true}]') == [
+        ("GPU-0", 0, 1, 8192, 100, "amd", 0, True, "", "AMD")]
+    # biren and vastai overwrite Devcore with 100 after the decode (biren/device.go:84, vastai/device.go:86): capacity_cores asks for it
+    for word in ("Biren", "Vastai"):
+        anno = '[{"id":"7-0","count":1,"devmem":32768,"type":"%s","health":true,"devicepairscore":{}}]' % word
+        assert run(word, abi.HS_REG_JSON, anno, cores=100) == [("7-0", 0, 1, 32768, 100, word, 0, True, "", word)]
+        assert run(word, abi.HS_REG_JSON, anno)[0][4] == 0                     # what the annotation itself says
+        for bad, msg in ((None, "annos not found"), (":", "invalid character"), ("", "unexpected end of JSON input"), ("[]", "no gpu found on node")):
+            with pytest.raises(eng.IngestError) as ei:
+                run(word, abi.HS_REG_JSON, bad, cores=100)
+            assert msg in str(ei.value), (bad, str(ei.value))
+    # whole-card GCUs come from the node's capacity
+    assert run("GCU", abi.HS_REG_CAPACITY_GCU, None, node="testnode", cores=2) == [
+        ("testnode-GCU-0", 0, 1, 100, 100, "GCU", 0, True, "", "GCU"), ("testnode-GCU-1", 1, 1, 100, 100, "GCU", 0, True, "", "GCU")]
+    with pytest.raises(eng.IngestError) as ei:
+        run("GCU", abi.HS_REG_CAPACITY_GCU, None, node="testnode", cores=0)
+    assert "device not found enflame.com/gcu" in str(ei.value)
