@@ -409,3 +409,28 @@ def test_metax_sgpu_vmemory_unit_rule():
     # Requests are not read at all (Limits only), and a lettered negative quantity lands below zero: the zero request
     assert product_generate([SGPU], {}, {"metax-tech.com/sgpu": quantity(1)}) == []
     assert product_generate([SGPU], sg(vmemory="-4Gi"), {}) == []
+
+
+def test_resourcereqs_per_container_sequences():
+    # pkg/scheduler/config/config_test.go:540-800 (Test_Resourcereqs) with device.Resourcereqs' loop (devices.go:639-690) on top of
+    # hs_generate_requests: custom NVIDIA resource names, a GPU container first / in the middle / last among plain ones
+    nv = dict(NVIDIA, count="hami.io/gpu", mem="hami.io/gpumem", pct="hami.io/gpumem-percentage", cores="hami.io/gpucores",
+              default_mem=0, default_cores=0)
+    gpu = {"hami.io/gpu": quantity(1), "hami.io/gpucores": quantity(30), "hami.io/gpumem": quantity(1000)}
+    cpu, mem = {"cpu": quantity(1)}, {"memory": quantity(2000)}
+    want = {"Nums": 1, "Type": "NVIDIA", "Memreq": 1000, "MemPercentagereq": 101, "Coresreq": 30}
+
+    def reqs(containers):           # PodDeviceRequests: one map per container, keyed by the vendor word
+        return [{r["key"]: strip(r) for r in product_generate([nv], limits, {})} for limits in containers]
+    assert reqs([cpu]) == [{}]
+    assert reqs([gpu]) == [{"NVIDIA": want}]
+    assert reqs([gpu, cpu]) == [{"NVIDIA": want}, {}]
+    assert reqs([gpu, cpu, mem]) == [{"NVIDIA": want}, {}, {}]
+    assert reqs([cpu, gpu, mem]) == [{}, {"NVIDIA": want}, {}]
+    assert reqs([cpu, mem, gpu]) == [{}, {}, {"NVIDIA": want}]
+    # several vendors configured at once: each container's map holds exactly the vendors it asks for
+    both = dict(gpu) | {"metax-tech.com/sgpu": quantity(1)}
+    got = reqs([both])                      # only NVIDIA is in the list handed in: the sGPU resource is not seen
+    assert got == [{"NVIDIA": want}]
+    got = [{r["key"]: strip(r) for r in product_generate([nv, SGPU], both, {})}]
+    assert set(got[0]) == {"NVIDIA", "Metax-SGPU"} and got[0]["NVIDIA"] == want and got[0]["Metax-SGPU"]["MemPercentagereq"] == 100
