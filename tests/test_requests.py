@@ -434,3 +434,24 @@ def test_resourcereqs_per_container_sequences():
     assert got == [{"NVIDIA": want}]
     got = [{r["key"]: strip(r) for r in product_generate([nv, SGPU], both, {})}]
     assert set(got[0]) == {"NVIDIA", "Metax-SGPU"} and got[0]["NVIDIA"] == want and got[0]["Metax-SGPU"]["MemPercentagereq"] == 100
+
+
+def test_nvidia_memory_factor_default_memory_and_zero_percentage():
+    # nvidia/device_test.go:1995-2053 (TestGenerateResourceRequests_MemoryFactor, …_DefaultMemory) and :2055-2093
+    # (TestZeroMemoryPercentageIsAccountedAsWholeCard, the request half; the Fit half is in test_oracle_manual_golden.py)
+    q = quantity
+    gen = lambda v, lim: strip((product_generate([v], lim, {}) or [None])[0])                       # noqa: E731
+    both = lambda v, lim: (gen(v, lim), strip(oracle_generate(v, lim, {})))                         # noqa: E731
+    f2 = dict(NVIDIA, factor=2)
+    got, ref = both(f2, {"nvidia.com/gpu": q(1), "nvidia.com/gpumem": q(1024)})
+    assert got == ref and got["Memreq"] == 2048
+    got, ref = both(f2, {"nvidia.com/gpu": q(1), "nvidia.com/gpumem": q({"_quantity": "1Gi"})})
+    assert got is None and ref is None                      # 2^30 x 2 leaves int32: the zero request
+    d512 = dict(NVIDIA, default_mem=512)
+    base, ref = both(d512, {"nvidia.com/gpu": q(1)})
+    assert base == ref and (base["Memreq"], base["MemPercentagereq"]) == (512, 101)
+    for extra in ({"nvidia.com/gpumem-percentage": (0, True, 0, 0, False)}, {"nvidia.com/gpumem": (0, True, 0, 0, False)}):
+        got, ref = both(d512, {"nvidia.com/gpu": q(1)} | extra)     # a 0 is "unset": it lands on the default like the absent key
+        assert got == ref == base, extra
+    got, ref = both(NVIDIA, {"nvidia.com/gpu": q(1), "nvidia.com/gpumem-percentage": (0, True, 0, 0, False)})
+    assert got == ref and (got["Memreq"], got["MemPercentagereq"]) == (0, 100)       # no default either: the whole card
