@@ -366,3 +366,18 @@ def test_allocated_annotation_is_metaxs_own_json():
     assert r["annotations"]["hami.io/metax-sgpu-devices-to-allocate"] == r["annotations"]["hami.io/metax-sgpu-devices-allocated"]
     assert QOS not in r["annotations"]        # the "best-effort" default is the webhook's (MutateAdmission, :89-129), not Filter's
     o.close()
+
+
+@pytest.mark.parametrize("node_policy,want", [("binpack", 600000.0), ("spread", -600000.0)])
+def test_override_score_weights_the_policy_neutral_term(node_policy, want):
+    # policy/node_policy_test.go:303-407 (TestOverrideScore, the two MetaX-SGPU cases): four idle cards of one MetaLink zone, a
+    # topology-aware pod takes two whole cards -> raw score 60 (scoreExclusiveDevices), weighted by +10000 under binpack and
+    # -10000 under spread on top of a default node score of 0
+    o = oa.Oracle(node_policy, "binpack")
+    o.node_upsert({"name": "node1", "devices": [
+        {"id": "GPU-%d" % (i + 1), "index": i, "count": 16, "devmem": 32768, "devcore": 100, "type": SGPU, "numa": 0, "mode": "",
+         "health": True, "vendor": SGPU, "sgpu": {"qos_policy": "", "link_zone": 1}} for i in range(4)]})
+    r = o.filter({"uid": "t", "ns": "default", "name": "t", "annotations": {TOPO: "true"},
+                  "containers": [[{"key": SGPU, "type": SGPU, "nums": 2, "memreq": 0, "mempct": 100, "coresreq": 100}]]})
+    assert r["status"] == abi.HS_FIT and r["score"] == want, r["score"]
+    o.close()

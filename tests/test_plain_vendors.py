@@ -607,3 +607,10 @@ def test_metax_table_parser_product_vs_oracle(orc):
                     assert abs(want) > 1e6, (doc, index, got, want)
                 checked += 1
     assert checked > 2000
+
+
+def test_override_score_metax_vectors(orc):
+    # policy/node_policy_test.go:217-302 (TestOverrideScore, the first two cases): two picks per vendor, DCU's ScoreNode adds 0,
+    # Metax-GPU's reads the node's topology losses ({"1":123,"2":321} -> 2000 - 321 under binpack); an unrelated annotation -> 0
+    assert _score_node(orc, 2, "binpack", losses='{"1":123,"2":321}') == 1679.0
+    assert _score_node(orc, 2, "binpack") == 0.0
