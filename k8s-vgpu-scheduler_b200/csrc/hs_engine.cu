@@ -92,36 +92,54 @@ bool checkType(const std::string* use, const std::string* nouse, const std::stri
 }
 
 // util.ParseDeviceScoringWeights, util/device_scoring_weights.go:58-102
-bool parseWeights(const std::string& value, int64_t w[3]) {
+// `why` receives the text after "invalid hami.io/device-scoring-weights annotation <value>: " (fmt's %q on the key where the
+// reference names it)
+std::string quoteGo(const std::string& s) {       // strconv.Quote for what an annotation can hold
+  std::string out = "\"";
+  for (unsigned char c : s) {
+    if (c == '"') out += "\\\"";
+    else if (c == '\\') out += "\\\\";
+    else if (c == '\n') out += "\\n";
+    else if (c == '\t') out += "\\t";
+    else if (c == '\r') out += "\\r";
+    else if (c < 0x20 || c == 0x7f) { char b[8]; snprintf(b, sizeof b, "\\x%02x", c); out += b; }
+    else out += (char)c;
+  }
+  return out + "\"";
+}
+bool parseWeights(const std::string& value, int64_t w[3], std::string& why) {
   w[0] = w[1] = w[2] = 0;
   auto parts = splitComma(value);
-  if (parts.size() != 3) return false;
+  if (parts.size() != 3) { why = "expected slot, core, and memory weights"; return false; }
   std::set<std::string> seen;
   for (auto& part : parts) {
     std::string p = trimSpace(part);
     size_t eq = p.find('=');
-    if (eq == std::string::npos) return false;
+    if (eq == std::string::npos) { why = "expected key=value entries"; return false; }
     std::string key = trimSpace(p.substr(0, eq)), val = trimSpace(p.substr(eq + 1));
-    if (seen.count(key)) return false;
-    if (val.empty()) return false;
+    if (seen.count(key)) { why = "duplicate " + quoteGo(key) + " weight"; return false; }
+    const std::string notInt = quoteGo(key) + " weight must be an integer";
+    if (val.empty()) { why = notInt; return false; }
     size_t i = 0;
     bool neg = false;
     if (val[0] == '+' || val[0] == '-') { neg = val[0] == '-'; i = 1; }
-    if (i >= val.size()) return false;
+    if (i >= val.size()) { why = notInt; return false; }
     unsigned long long acc = 0;
     for (; i < val.size(); i++) {
-      if (val[i] < '0' || val[i] > '9') return false;
+      if (val[i] < '0' || val[i] > '9') { why = notInt; return false; }
       unsigned long long d = (unsigned long long)(val[i] - '0');
-      if (acc > (0x8000000000000000ULL - d) / 10) return false;
+      if (acc > (0x8000000000000000ULL - d) / 10) { why = notInt; return false; }
       acc = acc * 10 + d;
     }
-    if (!neg && acc > 0x7fffffffffffffffULL) return false;
-    if (neg && acc != 0) return false;  // negative weight
+    if (!neg && acc > 0x7fffffffffffffffULL) { why = notInt; return false; }
+    if (neg && acc != 0) { why = quoteGo(key) + " weight must not be negative"; return false; }
     int64_t v = (int64_t)acc;
-    if (key == "slot") w[0] = v; else if (key == "core") w[1] = v; else if (key == "memory") w[2] = v; else return false;
+    if (key == "slot") w[0] = v; else if (key == "core") w[1] = v; else if (key == "memory") w[2] = v;
+    else { why = "unknown weight " + quoteGo(key); return false; }
     seen.insert(key);
   }
-  return !(w[0] == 0 && w[1] == 0 && w[2] == 0);
+  if (w[0] == 0 && w[1] == 0 && w[2] == 0) { why = "at least one weight must be positive"; return false; }
+  return true;
 }
 
 struct DevSlot {
@@ -667,7 +685,11 @@ int compile_pod(hs_handle* h, const hs_pod* pod, std::vector<uint32_t>& uuid_poo
   bool numaBind = get_anno(pod, "nvidia.com/numa-bind", tmp) && parseBoolTrue(tmp);
   int64_t w[3] = {1, 1, 1};
   if (get_anno(pod, "hami.io/device-scoring-weights", tmp)) {
-    if (!parseWeights(tmp, w)) { h->err = "invalid hami.io/device-scoring-weights annotation"; return HS_ERR_WEIGHTS; }
+    std::string why;
+    if (!parseWeights(tmp, w, why)) {      // the reference's text, util/device_scoring_weights.go:62-98
+      h->err = "invalid hami.io/device-scoring-weights annotation " + quoteGo(tmp) + ": " + why;
+      return HS_ERR_WEIGHTS;
+    }
   }
   DevPod& p = c.pod;
   p.op = OP_FILTER;

@@ -125,7 +125,31 @@ bool PolicyContains(const std::string& policy, const std::string& name) {
 }
 
 // pkg/util/device_scoring_weights.go:58-102
+// fmt's %q for the strings an annotation can hold: Go's strconv.Quote (printable text kept, the usual escapes, other bytes \xNN)
+static std::string goQuote(const std::string& s) {
+  std::string out = "\"";
+  for (unsigned char c : s) {
+    switch (c) {
+      case '"': out += "\\\""; break;
+      case '\\': out += "\\\\"; break;
+      case '\n': out += "\\n"; break;
+      case '\t': out += "\\t"; break;
+      case '\r': out += "\\r"; break;
+      default:
+        if (c < 0x20 || c == 0x7f) { char b[8]; snprintf(b, sizeof b, "\\x%02x", c); out += b; }
+        else out += (char)c;
+    }
+  }
+  return out + "\"";
+}
+static bool ParseDeviceScoringWeightsDetail(const std::string& value, DeviceScoringWeights& weights, std::string& err);
 bool ParseDeviceScoringWeights(const std::string& value, DeviceScoringWeights& weights, std::string& err) {
+  std::string detail;
+  if (ParseDeviceScoringWeightsDetail(value, weights, detail)) return true;
+  err = "invalid hami.io/device-scoring-weights annotation " + goQuote(value) + ": " + detail;   // device_scoring_weights.go:62-98
+  return false;
+}
+static bool ParseDeviceScoringWeightsDetail(const std::string& value, DeviceScoringWeights& weights, std::string& err) {
   weights = DeviceScoringWeights{0, 0, 0};
   std::set<std::string> seen;
   auto parts = Split(value, ',');
@@ -136,26 +160,27 @@ bool ParseDeviceScoringWeights(const std::string& value, DeviceScoringWeights& w
     if (eq == std::string::npos) { err = "expected key=value entries"; return false; }
     std::string key = TrimSpace(p.substr(0, eq));
     std::string val = TrimSpace(p.substr(eq + 1));
-    if (seen.count(key)) { err = "duplicate weight"; return false; }
+    if (seen.count(key)) { err = "duplicate " + goQuote(key) + " weight"; return false; }
     // strconv.ParseInt(val, 10, 64)
-    if (val.empty()) { err = "weight must be an integer"; return false; }
+    const std::string notInt = goQuote(key) + " weight must be an integer";
+    if (val.empty()) { err = notInt; return false; }
     size_t i = 0; bool neg = false;
     if (val[0] == '+' || val[0] == '-') { neg = val[0] == '-'; i = 1; }
-    if (i >= val.size()) { err = "weight must be an integer"; return false; }
+    if (i >= val.size()) { err = notInt; return false; }
     unsigned long long acc = 0;
     for (; i < val.size(); i++) {
-      if (val[i] < '0' || val[i] > '9') { err = "weight must be an integer"; return false; }
+      if (val[i] < '0' || val[i] > '9') { err = notInt; return false; }
       unsigned long long d = (unsigned long long)(val[i] - '0');
-      if (acc > (0x8000000000000000ULL - d) / 10) { err = "weight must be an integer"; return false; }
+      if (acc > (0x8000000000000000ULL - d) / 10) { err = notInt; return false; }
       acc = acc * 10 + d;
     }
-    if (!neg && acc > 0x7fffffffffffffffULL) { err = "weight must be an integer"; return false; }
+    if (!neg && acc > 0x7fffffffffffffffULL) { err = notInt; return false; }
     int64_t w = neg ? (int64_t)(0 - acc) : (int64_t)acc;
-    if (w < 0) { err = "weight must not be negative"; return false; }
+    if (w < 0) { err = goQuote(key) + " weight must not be negative"; return false; }
     if (key == "slot") weights.Slot = w;
     else if (key == "core") weights.Core = w;
     else if (key == "memory") weights.Memory = w;
-    else { err = "unknown weight"; return false; }
+    else { err = "unknown weight " + goQuote(key); return false; }
     seen.insert(key);
   }
   if (weights.Slot == 0 && weights.Core == 0 && weights.Memory == 0) { err = "at least one weight must be positive"; return false; }
