@@ -91,3 +91,52 @@ def test_assert_numa(orc, value, enforced):
     assert fit == (not enforced), (value, reason)
     if enforced:
         assert "NumaNotFit" in reason
+
+
+def test_one_container_two_device_types_keep_their_own_devices():
+    # score_test.go:4403-4446 (Test_fitInDevices_MultiTypePartition): one container asks for one device of each of two types on
+    # a node that holds both; each type's entry must list only its own device
+    from oracle_abi import abi
+    o = oa.Oracle()
+    o.node_upsert({"name": "node-1", "devices": [
+        {"id": "uuid-a", "index": 0, "count": 4, "devmem": 8192, "devcore": 100, "type": NV, "numa": 0, "mode": "hami-core", "health": True, "vendor": NV},
+        {"id": "uuid-b", "index": 1, "count": 4, "devmem": 8192, "devcore": 100, "type": "DCU", "numa": 0, "mode": "", "health": True, "vendor": "DCU"}]})
+    r = o.filter({"uid": "p", "ns": "default", "name": "p", "annotations": {}, "containers": [[
+        {"key": NV, "type": NV, "nums": 1, "memreq": 1024, "mempct": 101, "coresreq": 1},
+        {"key": "DCU", "type": "DCU", "nums": 1, "memreq": 1024, "mempct": 101, "coresreq": 1}]]})
+    assert r["status"] == abi.HS_FIT
+    assert {k: [[d[0] for d in c] for c in v] for k, v in r["devices"].items()} == {NV: [["uuid-a"]], "DCU": [["uuid-b"]]}
+    o.close()
+
+
+def test_stale_pod_device_allocations_touch_nothing():
+    # scheduler_test.go:175-395 (Test_getNodesUsage_StalePodDeviceAllocation): a cached pod that names a UUID the node no
+    # longer has adds no usage anywhere and leaves every real device healthy and schedulable; a valid one beside it still counts
+    from oracle_abi import abi
+
+    def fresh(devs):
+        o = oa.Oracle()
+        o.node_upsert({"name": "node1", "devices": [
+            {"id": u, "index": i + 1, "count": 10, "devmem": 1024, "devcore": 100, "type": NV, "numa": 1, "mode": "hami", "health": True,
+             "vendor": NV} for i, u in enumerate(devs)]})
+        return o
+    o = fresh(["GPU-B"])                                                    # StaleOnly
+    o.usage_apply("1111", "node1", "GPU-A", 1, 100, 10)
+    assert o.snapshot("node1") == [(0, 0, 0)]
+    o.close()
+    o = fresh(["GPU-B"])                                                    # ValidOnly
+    o.usage_apply("2222", "node1", "GPU-B", 1, 200, 20)
+    assert o.snapshot("node1") == [(1, 200, 20)]
+    o.close()
+    o = fresh(["GPU-B"])                                                    # MixedStaleAndValid
+    o.usage_apply("1111", "node1", "GPU-A", 1, 100, 10)
+    o.usage_apply("2222", "node1", "GPU-B", 1, 200, 20)
+    assert o.snapshot("node1") == [(1, 200, 20)]
+    o.close()
+    o = fresh(["GPU-B", "GPU-C"])                                           # MultipleDevices: a ghost UUID beside two real cards
+    o.usage_apply("3333", "node1", "GPU-GHOST", 1, 512, 50)
+    assert o.snapshot("node1") == [(0, 0, 0), (0, 0, 0)]
+    r = o.filter({"uid": "p", "ns": "default", "name": "p", "annotations": {}, "containers": [[
+        {"key": NV, "type": NV, "nums": 2, "memreq": 512, "mempct": 101, "coresreq": 10}]]})
+    assert r["status"] == abi.HS_FIT and sorted(d[0] for d in r["devices"][NV][0]) == ["GPU-B", "GPU-C"]     # both still healthy
+    o.close()
