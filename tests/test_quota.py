@@ -10,6 +10,8 @@ import ctypes as C
 import json
 import os
 
+import pytest
+
 import oracle_abi as oa
 from oracle_abi import abi
 
@@ -127,4 +129,30 @@ def test_filter_tracks_quota_usage_in_the_oracle():
         lim, used, st = quota_get(L, o, "default", "NVIDIA", MEM)
         assert 0 <= used <= 400000 and st
     assert fits > 5 and nofit_quota > 5
+    o.close()
+
+
+@pytest.mark.parametrize("nums,cores,mem,q_cores,q_mem,want", [
+    # pkg/scheduler/scheduler_test.go:2066-2370 (Test_ResourceQuota): node1 holds four cards of 2000 / 8000 / 4000 / 6000 MiB
+    (2, 100, 2000, 200, 4000, None),                                                             # "multi device Resourcequota pass"
+    (2, 60, 3000, 200, 4000, "1/4 AllocatedCardsInsufficientRequest, 3/4 ResourceQuotaNotFit"),  # the quota gate sits before the memory gate
+    (1, 0, 0, 100, 2000, None),                                                                  # unspecified -> a whole card; only the 2000 MiB one fits the quota
+    (1, 0, 0, 100, 1500, "4/4 ResourceQuotaNotFit"),
+], ids=["multi-pass", "multi-deny", "whole-card-pass", "whole-card-deny"])
+def test_resource_quota_filter_vectors(nums, cores, mem, q_cores, q_mem, want):
+    L = _lib()
+    o = oa.Oracle("binpack", "spread")           # NewScheduler()'s defaults: node policy binpack, GPU policy spread
+    o.node_upsert({"name": "node1", "devices": [
+        {"id": "device%d" % (i + 1), "index": i % 2, "count": 10, "devmem": m, "devcore": 100, "type": "NVIDIA", "numa": 0, "mode": "hami",
+         "health": True, "vendor": "NVIDIA"} for i, m in enumerate((2000, 8000, 4000, 6000))]})
+    L.oracle_quota_set(o.h, b"default", b"NVIDIA", CORE, q_cores)
+    L.oracle_quota_set(o.h, b"default", b"NVIDIA", MEM, q_mem)
+    r = o.filter({"uid": "t", "ns": "default", "name": "t", "annotations": {}, "containers": [[
+        {"key": "NVIDIA", "type": "NVIDIA", "nums": nums, "memreq": mem, "mempct": 100 if mem == 0 else 101, "coresreq": cores}]]})
+    if want is None:
+        assert r["status"] == abi.HS_FIT and r["node"] == "node1", r.get("failed")
+        if nums == 1:
+            assert [d[0] for d in r["devices"]["NVIDIA"][0]] == ["device1"]
+    else:
+        assert r["status"] == abi.HS_NOFIT and r["failed"] == {"node1": want}
     o.close()
