@@ -1216,13 +1216,13 @@ const std::string& fail_string_slow(hs_handle* h, const DevFail& f) {
   }
   else if (kind == FK_NODE_INSUFFICIENT) s = "NodeInsufficientDevice";
   else if (kind == FK_TYPE_NOT_FOUND) s = "Device type not found";
-  else if (kind == FK_HIST) {
+  else if (kind == FK_HIST || kind == FK_HIST_ZALLOC) {
     // common.GenReason, common/common.go:46-53
     std::vector<std::string> parts;
     char buf[96];
     for (int r = 0; r < HS_R_COUNT; r++) {
       uint32_t cnt = r < 8 ? (f.c0 >> (4 * r)) & 15u : (r < 16 ? (f.c1 >> (4 * (r - 8))) & 15u : (f.pad >> (4 * (r - 16))) & 15u);
-      if (!cnt) continue;
+      if (!cnt && !(kind == FK_HIST_ZALLOC && r == 12)) continue;      // a key the reference wrote with 0 is still printed
       snprintf(buf, sizeof buf, "%u/%u %s", cnt, cards, kReasonNames[r]);
       parts.push_back(buf);
     }

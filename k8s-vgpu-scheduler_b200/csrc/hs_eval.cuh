@@ -679,7 +679,10 @@ __device__ bool dev_fit(NodeWork& w, const DevPod& pod, const DevEntry& e, const
       }
     }
     if (nsel != origin) {
-      if (MODE == EV_EXPLAIN) { out.reasons[12] = (uint32_t)nsel; out.fcards = (uint32_t)origin; }
+      if (MODE == EV_EXPLAIN) {
+        out.reasons[12] = (uint32_t)nsel; out.fcards = (uint32_t)origin;
+        if (nsel == 0) out.fkind = FK_HIST_ZALLOC;      // the reference still lists "0/<request> AllocatedCardsInsufficientRequest"
+      }
       return false;
     }
     for (int t = 0; t < nsel; t++) { fc.tmp_dev[t] = sel_dev[t]; fc.tmp_mem[t] = sel_mem[t]; }

@@ -152,12 +152,13 @@ __device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v)
 __device__ __forceinline__ void pack_fail(const EvalOut& out, DevFail& f) {
   f.kind_cards = (out.fkind & 15u) | (out.fcards << 4);
   uint32_t c0 = 0, c1 = 0;
-  if (out.fkind == FK_HIST) {
+  const bool hist = out.fkind == FK_HIST || out.fkind == FK_HIST_ZALLOC;
+  if (hist) {
     for (int r = 0; r < 8; r++) c0 |= (out.reasons[r] & 15u) << (4 * r);
     for (int r = 8; r < 16; r++) c1 |= (out.reasons[r] & 15u) << (4 * (r - 8));
   }
   uint32_t c2 = 0;
-  if (out.fkind == FK_HIST)
+  if (hist)
     for (int r = 16; r < 24; r++) c2 |= (out.reasons[r] & 15u) << (4 * (r - 16));
   f.c0 = c0; f.c1 = c1; f.pad = c2;
 }

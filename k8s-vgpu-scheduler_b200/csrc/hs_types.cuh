@@ -232,7 +232,9 @@ struct DevDecision {        // 16 B header; rows live in the alloc pool
 
 // per-node failure record written only when a decision finds no node (common.go:46-53)
 enum { FK_NONE = 0, FK_HIST = 1, FK_NODE_INSUFFICIENT = 2, FK_TYPE_NOT_FOUND = 3, FK_NOT_CANDIDATE = 4,
-       FK_MIG_ADD_FAILED = 5 };   // AddResourceUsage returned an error (score.go:125-128): c0 = device slot, c1 = node slot
+       FK_MIG_ADD_FAILED = 5,
+       FK_HIST_ZALLOC = 6 };      // FK_HIST whose AllocatedCardsInsufficientRequest entry is present with a count of 0 (Ascend910C:
+                                  // ascend/device.go:585-588 writes len(combination) into the map even when it is 0)   // AddResourceUsage returned an error (score.go:125-128): c0 = device slot, c1 = node slot
 struct DevFail {            // 16 B
   uint32_t kind_cards;      // bits0-3 kind | bits4-31 cards denominator
   uint32_t c0;              // reasons 0-7, 4 bits each (HS_R_* order)
