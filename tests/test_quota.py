@@ -156,3 +156,21 @@ def test_resource_quota_filter_vectors(nums, cores, mem, q_cores, q_mem, want):
     else:
         assert r["status"] == abi.HS_NOFIT and r["failed"] == {"node1": want}
     o.close()
+
+
+def test_cambricon_whole_card_request_meets_the_memory_quota():
+    # cambricon/device_test.go:1317-1378 (TestDevices_Fit_ResourceQuotaWholeCardRequest): a request that names no memory is an
+    # implicit whole-card ask; its memory is resolved from the card BEFORE fitQuota, so a 40960 MiB card cannot pass a quota
+    # of limits.cambricon.com/mlu.smlu.vmemory: 50 (x MemoryFactor 256 = 12800 MiB)
+    L = _lib()
+    o = oa.Oracle("binpack", "spread")
+    o.node_upsert({"name": "node", "devices": [
+        {"id": "dev-0", "index": 0, "count": 100, "devmem": 40960, "devcore": 100, "type": "MLU", "numa": 0, "mode": "", "health": True, "vendor": "MLU"}]})
+    L.oracle_quota_set(o.h, b"cambricon-quota-test-ns", b"MLU", MEM, 50)
+    pod = {"uid": "w", "ns": "cambricon-quota-test-ns", "name": "w", "annotations": {}, "containers": [[
+        {"key": "MLU", "type": "MLU", "nums": 1, "memreq": 0, "mempct": 100, "coresreq": 10}]]}
+    r = o.filter(pod)
+    assert r["status"] == abi.HS_NOFIT and r["failed"] == {"node": "1/1 ResourceQuotaNotFit"}, r
+    r = o.filter(dict(pod, ns="another-namespace"))           # the quota is the namespace's
+    assert r["status"] == abi.HS_FIT
+    o.close()

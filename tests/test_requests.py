@@ -455,3 +455,19 @@ def test_nvidia_memory_factor_default_memory_and_zero_percentage():
         assert got == ref == base, extra
     got, ref = both(NVIDIA, {"nvidia.com/gpu": q(1), "nvidia.com/gpumem-percentage": (0, True, 0, 0, False)})
     assert got == ref and (got["Memreq"], got["MemPercentagereq"]) == (0, 100)       # no default either: the whole card
+
+
+def test_memory_factor_overflow_gives_the_zero_request():
+    # hygon/device_test.go:662-682 and ascend/device_test.go:1567-1624 (Test_GenerateResourceRequests_MemoryFactorOverflow): a value
+    # that fits int32 but leaves it once scaled by MemoryFactor yields the zero request, on ascend's soft-partition and trim paths alike
+    q = quantity
+    for v, lim in ((dict(DCU, factor=1024), {"hygon.com/dcunum": q(1), "hygon.com/dcumem": q(3000000)}),
+                   (dict(ASCEND_CORE, factor=10), {"huawei.com/Ascend910B3": q(1), "huawei.com/Ascend910B3-core": q(10),
+                                                   "huawei.com/Ascend910B3-memory": q(300000000)}),
+                   (dict(ASCEND_910A, factor=10), {"huawei.com/Ascend910A": q(1), "huawei.com/Ascend910A-memory": q(300000000)})):
+        assert product_generate([v], lim, {}) == [], v["word"]
+        ref = oracle_generate(v, lim, {})
+        assert ref is None or ref["Nums"] <= 0, v["word"]
+    # and just below the edge they still go through
+    got = product_generate([dict(DCU, factor=1024)], {"hygon.com/dcunum": q(1), "hygon.com/dcumem": q(2097151)}, {})
+    assert got and got[0]["Memreq"] == 2097151 * 1024
